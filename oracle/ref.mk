@@ -1,0 +1,139 @@
+# oracle/ref.mk - compiles the REFERENCE's own C++ sources, where they lie
+# under /root/reference, into oracle/_ref/ (git-ignored; travels to the GPU
+# box with the snapshot).  No reference source is copied into this repo: the
+# only files of ours that take part are the shims under oracle/shim/ (GSL
+# declarations, GUI/table stand-ins, OpenEXR config headers) and the drivers
+# oracle/raycast_ref.cpp / oracle/dumpscene_ref.cpp.
+# The reference's own CMake cannot configure here (OpenGL/glfw/GSL required,
+# SURVEY.md F11), so the source list below mirrors CMakeLists.txt:526-652
+# minus util/gui.cpp, the two missing table files and gpu/*.
+# TEST INFRASTRUCTURE ONLY - nothing here is linked into the product.
+#
+#   make -f oracle/ref.mk -j8         (from the repo root)
+REF   ?= /root/reference
+OUT   ?= oracle/_ref
+GEN   := $(OUT)/gen
+OBJ   := $(OUT)/obj
+CXX   := g++
+# -ffp-contract=off: the reference pins this for clang>=14 (CMakeLists.txt:136-139);
+# g++ would otherwise fuse a*b+c under -march with FMA.
+# x86-64-v3 rather than native so the binaries run on the GPU box's host CPU.
+OPT   := -O2 -march=x86-64-v3 -ffp-contract=off -fno-fast-math
+DEFS  := -DPBRT_IS_LINUX -DPBRT_HAVE_MMAP -DPBRT_HAVE_POSIX_MEMALIGN \
+         '-DPBRT_NOINLINE=__attribute__((noinline))' -DPBRT_RESTRICT=__restrict__ \
+         -DPTEX_STATIC -DNDEBUG
+EXT   := $(REF)/src/ext
+INCS  := -I$(REF)/src -I$(GEN) -Ioracle/shim -I$(EXT) \
+         -I$(EXT)/filesystem -I$(EXT)/double-conversion -I$(EXT)/stb \
+         -I$(EXT)/openvdb/nanovdb -I$(EXT)/eigen -I$(EXT)/ptex/src/ptex \
+         -I$(EXT)/glad/include -I$(EXT)/glfw/include -I$(EXT)/qoi \
+         -I$(EXT)/libdeflate -I$(EXT)/zlib -I$(EXT)/utf8proc -I$(EXT)/lodepng -I$(EXT)/rply \
+         -I$(EXT)/openexr/OpenEXR/IlmImf -I$(EXT)/openexr/IlmBase/Half \
+         -I$(EXT)/openexr/IlmBase/Iex -I$(EXT)/openexr/IlmBase/Imath \
+         -I$(EXT)/openexr/IlmBase/IlmThread
+CXXFLAGS := -std=c++17 $(OPT) $(DEFS) $(INCS) -w -pthread
+
+PBRT_TOP := bsdf bssrdf bxdfs cameras film filters interaction lights lightsamplers \
+            materials media options paramdict parser pbrt ray samplers scene shapes textures
+PBRT_CPU := cpu/aggregates cpu/integrators cpu/primitive cpu/render
+PBRT_WF  := wavefront/aggregate wavefront/camera wavefront/film wavefront/integrator \
+            wavefront/media wavefront/samples wavefront/surfscatter wavefront/subsurface \
+            wavefront/wavefront
+PBRT_UTIL := args buffercache check color colorspace display error file float image log \
+             loopsubdiv lowdiscrepancy math memory mesh mipmap noise parallel primes print \
+             progressreporter pstd rng sampling scattering sobolmatrices spectrum stats \
+             stbimage string transform vecmath
+PBRT_SRCS := $(PBRT_TOP) $(PBRT_CPU) $(PBRT_WF) $(addprefix util/,$(PBRT_UTIL))
+PBRT_OBJS := $(patsubst %,$(OBJ)/pbrt/%.o,$(PBRT_SRCS))
+RGB_OBJS  := $(patsubst %,$(OBJ)/gen/rgbspectrum_%.o,srgb dci_p3 rec2020 aces)
+
+DC_SRCS := bignum bignum-dtoa cached-powers double-to-string fast-dtoa fixed-dtoa string-to-double strtod
+DC_OBJS := $(patsubst %,$(OBJ)/ext/dc_%.o,$(DC_SRCS))
+PTEX_SRCS := PtexCache PtexFilters PtexHalf PtexReader PtexSeparableFilter PtexSeparableKernel \
+             PtexTriangleFilter PtexTriangleKernel PtexUtils PtexWriter
+PTEX_OBJS := $(patsubst %,$(OBJ)/ext/ptex_%.o,$(PTEX_SRCS))
+ZLIB_SRCS := adler32 compress crc32 deflate gzclose gzlib gzread gzwrite inflate infback inftrees inffast trees uncompr zutil
+ZLIB_OBJS := $(patsubst %,$(OBJ)/ext/z_%.o,$(ZLIB_SRCS))
+DEFL_SRCS := lib/adler32 lib/crc32 lib/deflate_compress lib/deflate_decompress lib/gzip_compress \
+             lib/gzip_decompress lib/utils lib/zlib_compress lib/zlib_decompress lib/x86/cpu_features
+DEFL_OBJS := $(patsubst %,$(OBJ)/ext/deflate_%.o,$(subst /,_,$(DEFL_SRCS)))
+EXT_OBJS := $(DC_OBJS) $(PTEX_OBJS) $(ZLIB_OBJS) $(DEFL_OBJS) $(OBJ)/ext/utf8proc.o \
+            $(OBJ)/ext/lodepng.o $(OBJ)/ext/rply.o
+SHIM_OBJS := $(OBJ)/shim/gsl_stubs.o $(OBJ)/shim/tables_stub.o $(OBJ)/shim/gui_stub.o $(OBJ)/shim/exr_stub.o
+
+LIB := $(OUT)/libpbrt_ref.a
+# EXR I/O (Imf::*) is left unresolved on purpose: the oracle writes PFM and raw
+# dumps, never EXR; calling it would fault.
+LDFLAGS := -pthread -no-pie -Wl,--unresolved-symbols=ignore-all
+
+all: $(OUT)/pbrt_ref $(OUT)/raycast_ref
+
+$(GEN)/soac: $(REF)/src/pbrt/cmd/soac.cpp
+	@mkdir -p $(GEN)
+	$(CXX) -std=c++17 -O2 -o $@ $<
+$(GEN)/pbrt_soa.h: $(GEN)/soac
+	$(GEN)/soac $(REF)/src/pbrt/pbrt.soa > $@
+$(GEN)/wavefront_workitems_soa.h: $(GEN)/soac
+	$(GEN)/soac $(REF)/src/pbrt/wavefront/workitems.soa > $@
+$(GEN)/rgb2spec_opt: $(REF)/src/pbrt/cmd/rgb2spec_opt.cpp
+	@mkdir -p $(GEN)
+	$(CXX) -std=c++17 -O2 -pthread -I$(REF)/src -o $@ $<
+$(GEN)/rgbspectrum_srgb.cpp: $(GEN)/rgb2spec_opt
+	$(GEN)/rgb2spec_opt 64 $@ sRGB
+$(GEN)/rgbspectrum_dci_p3.cpp: $(GEN)/rgb2spec_opt
+	$(GEN)/rgb2spec_opt 64 $@ DCI_P3
+$(GEN)/rgbspectrum_rec2020.cpp: $(GEN)/rgb2spec_opt
+	$(GEN)/rgb2spec_opt 64 $@ REC2020
+$(GEN)/rgbspectrum_aces.cpp: $(GEN)/rgb2spec_opt
+	$(GEN)/rgb2spec_opt 64 $@ ACES2065_1
+SOA := $(GEN)/pbrt_soa.h $(GEN)/wavefront_workitems_soa.h
+
+$(OBJ)/pbrt/%.o: $(REF)/src/pbrt/%.cpp $(SOA)
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+$(OBJ)/gen/%.o: $(GEN)/%.cpp
+	@mkdir -p $(dir $@)
+	$(CXX) -std=c++17 -O0 -w -c $< -o $@
+$(OBJ)/ext/dc_%.o: $(EXT)/double-conversion/double-conversion/%.cc
+	@mkdir -p $(dir $@)
+	$(CXX) -std=c++17 -O2 -w -c $< -o $@
+$(OBJ)/ext/ptex_%.o: $(EXT)/ptex/src/ptex/%.cpp
+	@mkdir -p $(dir $@)
+	$(CXX) -std=c++17 -O2 -w -DPTEX_STATIC -I$(EXT)/zlib -I$(EXT)/ptex/src/ptex -c $< -o $@
+$(OBJ)/ext/z_%.o: $(EXT)/zlib/%.c
+	@mkdir -p $(dir $@)
+	gcc -O2 -w -DHAVE_UNISTD_H -I$(EXT)/zlib -c $< -o $@
+define DEFL_RULE
+$(OBJ)/ext/deflate_$(subst /,_,$(1)).o: $(EXT)/libdeflate/$(1).c
+	@mkdir -p $$(dir $$@)
+	gcc -O2 -w -I$(EXT)/libdeflate -c $$< -o $$@
+endef
+$(foreach s,$(DEFL_SRCS),$(eval $(call DEFL_RULE,$(s))))
+$(OBJ)/ext/utf8proc.o: $(EXT)/utf8proc/utf8proc.c
+	@mkdir -p $(dir $@)
+	gcc -O2 -w -DUTF8PROC_STATIC -c $< -o $@
+$(OBJ)/ext/lodepng.o: $(EXT)/lodepng/lodepng.cpp
+	@mkdir -p $(dir $@)
+	$(CXX) -O2 -w -c $< -o $@
+$(OBJ)/ext/rply.o: $(EXT)/rply/rply.cpp
+	@mkdir -p $(dir $@)
+	$(CXX) -O2 -w -c $< -o $@
+$(OBJ)/shim/gsl_stubs.o: oracle/shim/gsl_stubs.c
+	@mkdir -p $(dir $@)
+	gcc -O2 -Ioracle/shim -c $< -o $@
+$(OBJ)/shim/%.o: oracle/shim/%.cpp $(SOA)
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+
+$(LIB): $(PBRT_OBJS) $(RGB_OBJS) $(EXT_OBJS) $(SHIM_OBJS)
+	rm -f $@ && ar rcs $@ $^
+
+$(OUT)/pbrt_ref: $(REF)/src/pbrt/cmd/pbrt.cpp $(LIB)
+	$(CXX) $(CXXFLAGS) $< $(LIB) $(LDFLAGS) -o $@
+# -Dprivate=public in this ONE translation unit lets the driver read
+# BVHAggregate::nodes / primitives (cpu/aggregates.h:66-69); layouts are
+# unchanged so it links against the normally-compiled library.
+$(OUT)/raycast_ref: oracle/raycast_ref.cpp $(LIB)
+	$(CXX) $(CXXFLAGS) $< $(LIB) $(LDFLAGS) -o $@
+
+.PHONY: all
