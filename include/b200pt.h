@@ -1,0 +1,174 @@
+/* b200pt.h - C ABI of the B200-native wavefront path-tracing backend for
+ * pbrt-v4 (ISET fork).  Plain pointers and sizes only; no C++/torch types.
+ *
+ * This is the drop-in boundary.  Each entry point names the
+ * reference interface it replaces (paths relative to the reference's src/pbrt):
+ *
+ *   b200pt_scene_create        CPUAggregate::CPUAggregate -> BasicScene::CreateAggregate
+ *                              (wavefront/aggregate.cpp:20-31, scene.cpp:1430-1596) and the
+ *                              BVHAggregate ctor / SAH build / flattenBVH
+ *                              (cpu/aggregates.cpp:140-190, 192-387, 505-522)
+ *   b200pt_scene_bounds        WavefrontAggregate::Bounds (wavefront/integrator.h:36,
+ *                              wavefront/aggregate.h:33)
+ *   b200pt_intersect_closest   WavefrontAggregate::IntersectClosest (wavefront/integrator.h:38-43,
+ *                              wavefront/aggregate.cpp:34-59) = BVHAggregate::Intersect
+ *                              (cpu/aggregates.cpp:529-579) over a ray batch
+ *   b200pt_intersect_any       WavefrontAggregate::IntersectShadow (wavefront/integrator.h:45-46,
+ *                              wavefront/aggregate.cpp:61-70) = BVHAggregate::IntersectP
+ *                              (cpu/aggregates.cpp:581-624) over a ray batch
+ *   b200pt_bvh2_build          BVHAggregate::buildRecursive + flattenBVH, host only
+ *   b200pt_render / film_*     RenderWavefront (wavefront/wavefront.cpp:14-70):
+ *                              WavefrontPathIntegrator::Render (wavefront/integrator.cpp:290-493)
+ *
+ * Conventions: every function returns 0 (B200PT_OK) or a B200PT_ERR_* code and
+ * never aborts or throws (the reference LOG_FATALs; this boundary is stricter).
+ * The caller owns every host buffer it passes; the library owns all device
+ * memory.  One context = one CUDA device + one stream; handles are not
+ * thread-safe, distinct handles are independent.  There is NO CPU fallback:
+ * without a usable sm_100 device, context creation fails with
+ * B200PT_ERR_NO_DEVICE and nothing else can be called.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PT_VERSION 100
+
+enum {
+    B200PT_OK = 0,
+    B200PT_ERR_INVALID = 1,   /* bad argument / malformed description */
+    B200PT_ERR_CUDA = 2,      /* a CUDA call failed; see b200pt_last_error */
+    B200PT_ERR_NO_DEVICE = 3, /* no CUDA device: there is no CPU path */
+    B200PT_ERR_NOMEM = 4
+};
+
+/* where a ray / hit buffer lives */
+enum { B200PT_MEM_HOST = 0, B200PT_MEM_DEVICE = 1 };
+
+typedef struct b200pt_ctx b200pt_ctx;
+typedef struct b200pt_scene b200pt_scene;
+
+/* One triangle mesh in render space (util/mesh.h:19-44: p[], vertexIndices[]).
+ * Its position in the meshes[] array is the reference's Triangle::meshIndex
+ * (shapes.cpp:280).  object < 0: part of the world; otherwise the id of the
+ * object definition (instanced geometry, scene.cpp:1527-1555) it belongs to. */
+typedef struct b200pt_mesh {
+    int32_t object;
+    uint32_t n_vertices;
+    uint32_t n_triangles;
+    const float *p;         /* 3 * n_vertices */
+    const int32_t *indices; /* 3 * n_triangles */
+} b200pt_mesh;
+
+/* One object instance (TransformedPrimitive, cpu/primitive.cpp:112-131).
+ * instanceId reported in hits = 1 + index in instances[] (scene.cpp:1560-1573). */
+typedef struct b200pt_instance {
+    uint32_t object;
+    float render_from_instance[16]; /* row major 4x4: Transform::m    (util/transform.h) */
+    float instance_from_render[16]; /* its inverse as the host holds it: Transform::mInv */
+} b200pt_instance;
+
+/* A binary BVH handed over by the host in the reference's own flat layout
+ * (LinearBVHNode, cpu/aggregates.cpp:129-137: 32 B = bounds 24 B, i32
+ * primitivesOffset | secondChildOffset, u16 nPrimitives, u8 axis, pad).
+ * prims: 3 u32 per ordered primitive {kind, a, b}: kind 0 = triangle
+ * (a = mesh, b = tri); kind 1 = instance (a = instanceId, 1-based). */
+typedef struct b200pt_bvh2 {
+    int32_t object; /* -1 = top level */
+    uint32_t n_nodes;
+    uint32_t n_prims;
+    const void *nodes;
+    const uint32_t *prims;
+} b200pt_bvh2;
+
+typedef struct b200pt_scene_desc {
+    uint32_t n_meshes;
+    const b200pt_mesh *meshes;
+    uint32_t n_instances;
+    const b200pt_instance *instances;
+    /* n_bvhs == 0: the library builds the trees itself with the reference's
+     * SAH decisions (top level maxPrimsInNode 4, object level 1).  Otherwise
+     * one entry per BVH (top level + every object), e.g. read out of the
+     * host's BVHAggregate objects. */
+    uint32_t n_bvhs;
+    const b200pt_bvh2 *bvhs;
+    uint32_t flags; /* reserved, 0 */
+} b200pt_scene_desc;
+
+/* Closest-hit record.  miss: mesh == 0xFFFFFFFF.  (mesh, prim) =
+ * Triangle{meshIndex, triIndex} (shapes.h:1188); instance = instanceId or 0;
+ * t, b1, b2 = TriangleIntersection{t, b1, b2} (shapes.cpp:247-272), bit-exact. */
+typedef struct b200pt_hit {
+    uint32_t mesh;
+    uint32_t prim;
+    uint32_t instance;
+    float t;
+    float b1;
+    float b2;
+} b200pt_hit;
+
+typedef struct b200pt_scene_stats {
+    uint64_t n_triangles;   /* unique triangles resident */
+    uint64_t n_instances;
+    uint64_t n_bvh2_nodes;  /* all trees */
+    uint64_t n_wide_nodes;  /* device wide-BVH nodes, all trees */
+    uint64_t device_bytes;  /* HBM held by the scene */
+    double build_seconds;   /* host SAH build + flatten */
+    double upload_seconds;
+} b200pt_scene_stats;
+
+/* Per-call trace counters (the reference's "BVH/Nodes visited" cpu/aggregates.cpp:27,577
+ * and "Ray-Triangle intersection tests" shapes.cpp:148), filled only when
+ * B200PT_TRACE_COUNTERS is passed; the counting kernel variant is slower. */
+typedef struct b200pt_trace_stats {
+    uint64_t rays;
+    uint64_t nodes_visited;
+    uint64_t leaves_visited;
+    uint64_t prims_tested;
+    float kernel_ms; /* CUDA-event time of the traversal kernel(s) of the last call */
+} b200pt_trace_stats;
+
+enum { B200PT_TRACE_COUNTERS = 1u << 8 };
+
+int b200pt_version(void);
+int b200pt_device_count(int *count);
+int b200pt_context_create(int device, b200pt_ctx **out);
+/* run on an existing CUDA stream (cudaStream_t passed as void*); NULL = own stream */
+int b200pt_context_set_stream(b200pt_ctx *ctx, void *cuda_stream);
+int b200pt_context_sync(b200pt_ctx *ctx);
+int b200pt_context_destroy(b200pt_ctx *ctx);
+/* message of the last failure on this context (or of the last failed create when ctx == NULL) */
+const char *b200pt_last_error(const b200pt_ctx *ctx);
+
+int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_scene **out);
+int b200pt_scene_destroy(b200pt_scene *scene);
+int b200pt_scene_bounds(const b200pt_scene *scene, float bounds_min_max[6]);
+int b200pt_scene_get_stats(const b200pt_scene *scene, b200pt_scene_stats *out);
+
+/* rays: n x 7 floats {o.xyz, d.xyz, tMax}; hits: n records; occluded: n bytes (0/1).
+ * mem: B200PT_MEM_HOST (copied through pinned staging inside the call, the call
+ * returns after the results are in `hits`) or B200PT_MEM_DEVICE (asynchronous on
+ * the context's stream), optionally or-ed with B200PT_TRACE_COUNTERS. */
+int b200pt_intersect_closest(b200pt_scene *scene, const float *rays, int64_t n,
+                             b200pt_hit *hits, uint32_t mem);
+int b200pt_intersect_any(b200pt_scene *scene, const float *rays, int64_t n,
+                         uint8_t *occluded, uint32_t mem);
+int b200pt_get_trace_stats(const b200pt_scene *scene, b200pt_trace_stats *out);
+
+/* Host-only: build the binary SAH BVH for one primitive list exactly as the
+ * reference does (cpu/aggregates.cpp:192-387, 505-522) and return it in the
+ * LinearBVHNode layout.  bounds: n x 6 floats (pMin, pMax).  nodes_out must
+ * hold 2n-1 nodes of 32 B; order_out n indices into the input list (the
+ * reference's ordered `primitives`, leaves in depth-first order).  Needs no GPU. */
+int b200pt_bvh2_build(const float *bounds, uint32_t n, int max_prims_in_node,
+                      void *nodes_out, uint32_t *n_nodes_out, uint32_t *order_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_H */

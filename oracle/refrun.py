@@ -1,0 +1,71 @@
+"""oracle/refrun.py - runs the compiled reference (oracle/_ref/raycast_ref, pbrt_ref).
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs; never by the product package."""
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(HERE, "_ref")
+RAYCAST = os.path.join(REF_DIR, "raycast_ref")
+PBRT = os.path.join(REF_DIR, "pbrt_ref")
+
+REF_HIT_DTYPE = np.dtype([("mesh", "<u4"), ("prim", "<u4"), ("instance", "<u4"), ("t", "<f4"),
+                          ("uv", "<f4", 2), ("p", "<f4", 3), ("n", "<f4", 3)])
+NODE32_DTYPE = np.dtype([("bmin", "<f4", 3), ("bmax", "<f4", 3), ("offset", "<i4"),
+                         ("nprims", "<u2"), ("axis", "u1"), ("pad", "u1")])
+
+
+def available():
+    return os.access(RAYCAST, os.X_OK)
+
+
+def _run(args, timeout=3600):
+    r = subprocess.run(args, capture_output=True, text=True, timeout=timeout)
+    if r.returncode != 0:
+        raise RuntimeError(f"{' '.join(args)} failed ({r.returncode}): {r.stderr[-2000:]}")
+    lines = [l for l in r.stdout.strip().splitlines() if l.startswith("{")]
+    return json.loads(lines[-1]) if lines else {}
+
+
+class RefScene:
+    """A scene file on disk + the reference driver."""
+
+    def __init__(self, scene, workdir=None):
+        self._tmp = None
+        if workdir is None:
+            self._tmp = tempfile.TemporaryDirectory(prefix="b2ref_")
+            workdir = self._tmp.name
+        self.dir = workdir
+        self.path = os.path.join(workdir, "scene.b2sc")
+        scene.write(self.path)
+
+    def closest(self, rays, nthreads=0, reps=1):
+        rp, hp = os.path.join(self.dir, "rays.f32"), os.path.join(self.dir, "hits.bin")
+        np.ascontiguousarray(rays, dtype="<f4").tofile(rp)
+        info = _run([RAYCAST, self.path, "closest", rp, hp, str(nthreads), str(reps)])
+        return np.fromfile(hp, dtype=REF_HIT_DTYPE), info
+
+    def any(self, rays, nthreads=0, reps=1):
+        rp, hp = os.path.join(self.dir, "rays.f32"), os.path.join(self.dir, "occ.u8")
+        np.ascontiguousarray(rays, dtype="<f4").tofile(rp)
+        info = _run([RAYCAST, self.path, "any", rp, hp, str(nthreads), str(reps)])
+        return np.fromfile(hp, dtype=np.uint8), info
+
+    def dump_bvh(self):
+        """-> list of (object, nodes[NODE32_DTYPE], prims (n,3) u4) as the reference built them."""
+        out = os.path.join(self.dir, "bvh.bin")
+        _run([RAYCAST, self.path, "dump-bvh", out])
+        trees = []
+        with open(out, "rb") as f:
+            nb = int(np.fromfile(f, dtype="<u4", count=1)[0])
+            for _ in range(nb):
+                obj = int(np.fromfile(f, dtype="<i4", count=1)[0])
+                nn, npr = (int(x) for x in np.fromfile(f, dtype="<u4", count=2))
+                nodes = np.fromfile(f, dtype=NODE32_DTYPE, count=nn)
+                prims = np.fromfile(f, dtype="<u4", count=3 * npr).reshape(-1, 3)
+                trees.append((obj, nodes, prims))
+        return trees

@@ -1,0 +1,70 @@
+"""Builds libb200pt.so (the C-ABI library of include/b200pt.h) in-tree.
+
+nvcc cross-compiles sm_100a without a GPU.  Host translation units go through
+g++ with -ffp-contract=off (the SAH builder must reproduce the reference's float
+decisions); traversal .cu files use --fmad=false on top of explicit rn-intrinsics.
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
+LIB = os.path.join(HERE, "libb200pt.so")
+
+NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+CUDA_HOME = os.path.dirname(os.path.dirname(NVCC))
+GENCODE = ["-gencode", "arch=compute_100a,code=sm_100a"]
+
+CPP_SOURCES = ["bvh2_build.cpp", "scene_host.cpp", "api.cpp"]
+# (file, extra nvcc flags)
+CU_SOURCES = [
+    ("traverse_bvh2.cu", ["--fmad=false"]),
+]
+
+
+def _newer(src, dst, extra_deps):
+    if not os.path.exists(dst):
+        return True
+    t = os.path.getmtime(dst)
+    return any(os.path.getmtime(p) > t for p in [src] + extra_deps)
+
+
+def _run(cmd, verbose):
+    if verbose:
+        print(" ".join(cmd), flush=True)
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("build failed: " + " ".join(cmd))
+    if verbose and (r.stdout or r.stderr):
+        print(r.stdout + r.stderr, flush=True)
+
+
+def build(verbose=False, force=False):
+    os.makedirs(OBJ, exist_ok=True)
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".h")]
+    headers.append(os.path.join(os.path.dirname(HERE), "include", "b200pt.h"))
+    objs = []
+    for f in CPP_SOURCES:
+        src, obj = os.path.join(CSRC, f), os.path.join(OBJ, f + ".o")
+        objs.append(obj)
+        if force or _newer(src, obj, headers):
+            _run(["g++", "-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-fno-fast-math",
+                  "-march=x86-64-v3", "-Wall", "-I" + os.path.join(CUDA_HOME, "include"),
+                  "-c", src, "-o", obj], verbose)
+    for f, extra in CU_SOURCES:
+        src, obj = os.path.join(CSRC, f), os.path.join(OBJ, f + ".o")
+        objs.append(obj)
+        if force or _newer(src, obj, headers):
+            _run([NVCC, "-std=c++17", "-O3", "-lineinfo", "-Xptxas", "-v", "-Xcompiler", "-fPIC",
+                  "-Xcompiler", "-ffp-contract=off"] + GENCODE + extra + ["-c", src, "-o", obj], verbose)
+    if force or any(_newer(o, LIB, []) for o in objs):
+        _run([NVCC, "-shared", "-o", LIB] + objs + GENCODE + ["-cudart", "static"], verbose)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(verbose=True, force="--force" in sys.argv))

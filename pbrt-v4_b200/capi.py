@@ -1,0 +1,118 @@
+"""ctypes binding of include/b200pt.h (the same stub a maintainer would use from
+Python; the C++ reference binds the identical symbols directly)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb200pt.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_NOMEM = 0, 1, 2, 3, 4
+MEM_HOST, MEM_DEVICE = 0, 1
+TRACE_COUNTERS = 1 << 8
+MISS = 0xFFFFFFFF
+
+HIT_DTYPE = np.dtype([("mesh", "<u4"), ("prim", "<u4"), ("instance", "<u4"),
+                      ("t", "<f4"), ("b1", "<f4"), ("b2", "<f4")])
+NODE32_DTYPE = np.dtype([("bmin", "<f4", 3), ("bmax", "<f4", 3), ("offset", "<i4"),
+                         ("nprims", "<u2"), ("axis", "u1"), ("pad", "u1")])
+assert HIT_DTYPE.itemsize == 24 and NODE32_DTYPE.itemsize == 32
+
+
+class Mesh(C.Structure):
+    _fields_ = [("object", C.c_int32), ("n_vertices", C.c_uint32), ("n_triangles", C.c_uint32),
+                ("p", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_int32))]
+
+
+class Instance(C.Structure):
+    _fields_ = [("object", C.c_uint32), ("render_from_instance", C.c_float * 16),
+                ("instance_from_render", C.c_float * 16)]
+
+
+class BVH2(C.Structure):
+    _fields_ = [("object", C.c_int32), ("n_nodes", C.c_uint32), ("n_prims", C.c_uint32),
+                ("nodes", C.c_void_p), ("prims", C.POINTER(C.c_uint32))]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("n_meshes", C.c_uint32), ("meshes", C.POINTER(Mesh)),
+                ("n_instances", C.c_uint32), ("instances", C.POINTER(Instance)),
+                ("n_bvhs", C.c_uint32), ("bvhs", C.POINTER(BVH2)), ("flags", C.c_uint32)]
+
+
+class SceneStats(C.Structure):
+    _fields_ = [("n_triangles", C.c_uint64), ("n_instances", C.c_uint64), ("n_bvh2_nodes", C.c_uint64),
+                ("n_wide_nodes", C.c_uint64), ("device_bytes", C.c_uint64),
+                ("build_seconds", C.c_double), ("upload_seconds", C.c_double)]
+
+
+class TraceStats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("leaves_visited", C.c_uint64),
+                ("prims_tested", C.c_uint64), ("kernel_ms", C.c_float)]
+
+
+# every symbol include/b200pt.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "b200pt_version": (C.c_int, []),
+    "b200pt_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "b200pt_context_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "b200pt_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b200pt_context_sync": (C.c_int, [C.c_void_p]),
+    "b200pt_context_destroy": (C.c_int, [C.c_void_p]),
+    "b200pt_last_error": (C.c_char_p, [C.c_void_p]),
+    "b200pt_scene_create": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc), C.POINTER(C.c_void_p)]),
+    "b200pt_scene_destroy": (C.c_int, [C.c_void_p]),
+    "b200pt_scene_bounds": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "b200pt_scene_get_stats": (C.c_int, [C.c_void_p, C.POINTER(SceneStats)]),
+    "b200pt_intersect_closest": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint32]),
+    "b200pt_intersect_any": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint32]),
+    "b200pt_get_trace_stats": (C.c_int, [C.c_void_p, C.POINTER(TraceStats)]),
+    "b200pt_bvh2_build": (C.c_int, [C.POINTER(C.c_float), C.c_uint32, C.c_int, C.c_void_p,
+                                    C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+}
+
+_lib = None
+
+
+class B200PTError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"b200pt error {code}: {msg}")
+        self.code = code
+
+
+def lib():
+    """Loads libb200pt.so; fails loudly (no fallback) when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B200PTError(-1, f"{LIB_PATH} is missing - run `python -c 'import __graft_entry__ as g; g.build()'`; "
+                                  "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(code, ctx=None):
+    if code != OK:
+        msg = lib().b200pt_last_error(ctx)
+        raise B200PTError(code, (msg or b"").decode())
+
+
+def fptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def bvh2_build(boxes, max_prims_in_node=4):
+    """Host-only SAH build (no GPU): boxes (n,6) float32 -> (nodes[NODE32_DTYPE], order[u4])."""
+    boxes = np.ascontiguousarray(boxes, dtype=np.float32).reshape(-1, 6)
+    n = boxes.shape[0]
+    nodes = np.zeros(max(2 * n - 1, 1), dtype=NODE32_DTYPE)
+    order = np.zeros(n, dtype=np.uint32)
+    nn = C.c_uint32(0)
+    check(lib().b200pt_bvh2_build(fptr(boxes), n, int(max_prims_in_node), nodes.ctypes.data,
+                                  C.byref(nn), order.ctypes.data_as(C.POINTER(C.c_uint32))))
+    return nodes[:nn.value].copy(), order

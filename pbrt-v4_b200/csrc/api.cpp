@@ -1,0 +1,314 @@
+// api.cpp - the extern "C" boundary declared in include/b200pt.h.
+// Host code only; kernels are reached through kernels.h.  No CPU fallback
+// exists anywhere below: if there is no device, context creation fails.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/b200pt.h"
+#include "bvh2.h"
+#include "device_scene.h"
+#include "kernels.h"
+#include "scene_host.h"
+
+using namespace b200pt;
+
+struct b200pt_ctx {
+    int device = 0;
+    int smCount = 0;
+    cudaStream_t stream = nullptr;
+    bool ownStream = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    // grow-only device staging for host-pointer calls
+    void *dIn = nullptr;
+    size_t dInCap = 0;
+    void *dOut = nullptr;
+    size_t dOutCap = 0;
+    unsigned long long *dCounters = nullptr;
+};
+
+struct b200pt_scene {
+    b200pt_ctx *ctx = nullptr;
+    HostScene host;
+    DeviceScene dev{};
+    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr;
+    b200pt_scene_stats stats{};
+    b200pt_trace_stats trace{};
+};
+
+static std::string g_createErr;
+
+#define B2_CUDA(ctx, call)                                                                  \
+    do {                                                                                    \
+        cudaError_t e_ = (call);                                                            \
+        if (e_ != cudaSuccess) {                                                            \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                \
+            return B200PT_ERR_CUDA;                                                         \
+        }                                                                                   \
+    } while (0)
+
+extern "C" {
+
+int b200pt_version(void) { return B200PT_VERSION; }
+
+int b200pt_device_count(int *count) {
+    if (!count) return B200PT_ERR_INVALID;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        n = 0;
+    }
+    *count = n;
+    return B200PT_OK;
+}
+
+int b200pt_context_create(int device, b200pt_ctx **out) {
+    if (!out) return B200PT_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        (void)cudaGetLastError();
+        g_createErr = "no CUDA device visible; b200pt has no CPU path";
+        return B200PT_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= n) {
+        g_createErr = "device index out of range";
+        return B200PT_ERR_INVALID;
+    }
+    b200pt_ctx *c = new (std::nothrow) b200pt_ctx;
+    if (!c) return B200PT_ERR_NOMEM;
+    c->device = device;
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        g_createErr = std::string("cudaSetDevice: ") + cudaGetErrorString(cudaGetLastError());
+        delete c;
+        return B200PT_ERR_CUDA;
+    }
+    if (prop.major < 10) {
+        g_createErr = "device is not sm_100 class; b200pt ships sm_100a code only";
+        delete c;
+        return B200PT_ERR_NO_DEVICE;
+    }
+    c->smCount = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
+        cudaMalloc((void **)&c->dCounters, 8 * sizeof(unsigned long long)) != cudaSuccess) {
+        g_createErr = std::string("context setup: ") + cudaGetErrorString(cudaGetLastError());
+        delete c;
+        return B200PT_ERR_CUDA;
+    }
+    c->ownStream = true;
+    *out = c;
+    return B200PT_OK;
+}
+
+int b200pt_context_set_stream(b200pt_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return B200PT_ERR_INVALID;
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->ownStream) {
+        cudaStreamDestroy(ctx->stream);
+        ctx->ownStream = false;
+    }
+    if (cuda_stream) {
+        ctx->stream = (cudaStream_t)cuda_stream;
+    } else {
+        B2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        ctx->ownStream = true;
+    }
+    return B200PT_OK;
+}
+
+int b200pt_context_sync(b200pt_ctx *ctx) {
+    if (!ctx) return B200PT_ERR_INVALID;
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200PT_OK;
+}
+
+int b200pt_context_destroy(b200pt_ctx *ctx) {
+    if (!ctx) return B200PT_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->dIn) cudaFree(ctx->dIn);
+    if (ctx->dOut) cudaFree(ctx->dOut);
+    if (ctx->dCounters) cudaFree(ctx->dCounters);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->ownStream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return B200PT_OK;
+}
+
+const char *b200pt_last_error(const b200pt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_createErr.c_str(); }
+
+int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_scene **out) {
+    if (!ctx || !out) return B200PT_ERR_INVALID;
+    *out = nullptr;
+    b200pt_scene *s = new (std::nothrow) b200pt_scene;
+    if (!s) return B200PT_ERR_NOMEM;
+    s->ctx = ctx;
+    int rc = AssembleScene(desc, s->host, ctx->err);
+    if (rc != B200PT_OK) {
+        delete s;
+        return rc;
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    HostScene &h = s->host;
+    size_t nodeBytes = h.nodes.size() * sizeof(Node32), primBytes = h.prims.size() * sizeof(PrimSlot);
+    cudaError_t e = cudaSetDevice(ctx->device);
+    if (e == cudaSuccess) e = cudaMalloc(&s->dNodes, nodeBytes);
+    if (e == cudaSuccess) e = cudaMalloc(&s->dPrims, primBytes);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s->dNodes, h.nodes.data(), nodeBytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s->dPrims, h.prims.data(), primBytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) {
+        ctx->err = std::string("scene upload: ") + cudaGetErrorString(e);
+        b200pt_scene_destroy(s);
+        return e == cudaErrorMemoryAllocation ? B200PT_ERR_NOMEM : B200PT_ERR_CUDA;
+    }
+    s->dev.nodes = s->dNodes;
+    s->dev.prims = s->dPrims;
+    s->dev.instances = nullptr;
+    s->dev.rootNode = h.rootNode;
+    s->dev.nNodes = uint32_t(h.nodes.size());
+    s->dev.nPrims = uint32_t(h.prims.size());
+    s->dev.nInstances = 0;
+    s->stats.n_triangles = h.nTriangles;
+    s->stats.n_instances = 0;
+    s->stats.n_bvh2_nodes = h.nodes.size();
+    s->stats.n_wide_nodes = 0;
+    s->stats.device_bytes = nodeBytes + primBytes;
+    s->stats.build_seconds = h.buildSeconds;
+    s->stats.upload_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    *out = s;
+    return B200PT_OK;
+}
+
+int b200pt_scene_destroy(b200pt_scene *s) {
+    if (!s) return B200PT_OK;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    if (s->dNodes) cudaFree(s->dNodes);
+    if (s->dPrims) cudaFree(s->dPrims);
+    if (s->dInst) cudaFree(s->dInst);
+    delete s;
+    return B200PT_OK;
+}
+
+int b200pt_scene_bounds(const b200pt_scene *s, float b[6]) {
+    if (!s || !b) return B200PT_ERR_INVALID;
+    std::memcpy(b, s->host.bounds, 24);
+    return B200PT_OK;
+}
+
+int b200pt_scene_get_stats(const b200pt_scene *s, b200pt_scene_stats *out) {
+    if (!s || !out) return B200PT_ERR_INVALID;
+    *out = s->stats;
+    return B200PT_OK;
+}
+
+static int EnsureStaging(b200pt_ctx *ctx, size_t inBytes, size_t outBytes) {
+    if (inBytes > ctx->dInCap) {
+        if (ctx->dIn) cudaFree(ctx->dIn);
+        ctx->dIn = nullptr;
+        ctx->dInCap = 0;
+        B2_CUDA(ctx, cudaMalloc(&ctx->dIn, inBytes));
+        ctx->dInCap = inBytes;
+    }
+    if (outBytes > ctx->dOutCap) {
+        if (ctx->dOut) cudaFree(ctx->dOut);
+        ctx->dOut = nullptr;
+        ctx->dOutCap = 0;
+        B2_CUDA(ctx, cudaMalloc(&ctx->dOut, outBytes));
+        ctx->dOutCap = outBytes;
+    }
+    return B200PT_OK;
+}
+
+static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, uint32_t mem, bool any) {
+    if (!s || n < 0 || (n > 0 && (!rays || !out))) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = s->ctx;
+    const bool device = (mem & 0xFF) == B200PT_MEM_DEVICE;
+    const bool count = (mem & B200PT_TRACE_COUNTERS) != 0;
+    if ((mem & 0xFF) > B200PT_MEM_DEVICE) {
+        ctx->err = "unknown memory kind";
+        return B200PT_ERR_INVALID;
+    }
+    s->trace = b200pt_trace_stats{};
+    s->trace.rays = uint64_t(n);
+    if (n == 0) return B200PT_OK;
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t outRec = any ? 1 : sizeof(b200pt_hit);
+    const float *dRays = rays;
+    void *dOut = out;
+    if (!device) {
+        int rc = EnsureStaging(ctx, size_t(n) * 28, size_t(n) * outRec);
+        if (rc != B200PT_OK) return rc;
+        B2_CUDA(ctx, cudaMemcpyAsync(ctx->dIn, rays, size_t(n) * 28, cudaMemcpyHostToDevice, ctx->stream));
+        dRays = (const float *)ctx->dIn;
+        dOut = ctx->dOut;
+    }
+    if (count) B2_CUDA(ctx, cudaMemsetAsync(ctx->dCounters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    B2_CUDA(ctx, LaunchTraverseBVH2(s->dev, dRays, n, any ? nullptr : (b200pt_hit *)dOut,
+                                    any ? (unsigned char *)dOut : nullptr, any,
+                                    count ? ctx->dCounters : nullptr, ctx->smCount, ctx->stream));
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (!device) {
+        B2_CUDA(ctx, cudaMemcpyAsync(out, dOut, size_t(n) * outRec, cudaMemcpyDeviceToHost, ctx->stream));
+        B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    if (count) {
+        unsigned long long c[8];
+        B2_CUDA(ctx, cudaMemcpyAsync(c, ctx->dCounters, sizeof c, cudaMemcpyDeviceToHost, ctx->stream));
+        B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        s->trace.nodes_visited = c[0];
+        s->trace.leaves_visited = c[1];
+        s->trace.prims_tested = c[2];
+    }
+    return B200PT_OK;
+}
+
+int b200pt_intersect_closest(b200pt_scene *s, const float *rays, int64_t n, b200pt_hit *hits, uint32_t mem) {
+    return Intersect(s, rays, n, hits, mem, false);
+}
+
+int b200pt_intersect_any(b200pt_scene *s, const float *rays, int64_t n, uint8_t *occluded, uint32_t mem) {
+    return Intersect(s, rays, n, occluded, mem, true);
+}
+
+int b200pt_get_trace_stats(const b200pt_scene *s, b200pt_trace_stats *out) {
+    if (!s || !out) return B200PT_ERR_INVALID;
+    b200pt_scene *ms = const_cast<b200pt_scene *>(s);
+    // kernel time of the last call (waits for it)
+    if (s->trace.rays && cudaEventSynchronize(s->ctx->ev1) == cudaSuccess) {
+        float ms_ = 0;
+        if (cudaEventElapsedTime(&ms_, s->ctx->ev0, s->ctx->ev1) == cudaSuccess)
+            ms->trace.kernel_ms = ms_;
+    }
+    (void)cudaGetLastError();
+    *out = s->trace;
+    return B200PT_OK;
+}
+
+int b200pt_bvh2_build(const float *bounds, uint32_t n, int max_prims_in_node, void *nodes_out,
+                      uint32_t *n_nodes_out, uint32_t *order_out) {
+    if (!bounds || !n || !nodes_out || !n_nodes_out || !order_out || max_prims_in_node < 1)
+        return B200PT_ERR_INVALID;
+    std::vector<Node32> nodes;
+    std::vector<uint32_t> order;
+    BuildBVH2(reinterpret_cast<const Box *>(bounds), n, max_prims_in_node, nodes, order);
+    std::memcpy(nodes_out, nodes.data(), nodes.size() * sizeof(Node32));
+    std::memcpy(order_out, order.data(), order.size() * sizeof(uint32_t));
+    *n_nodes_out = uint32_t(nodes.size());
+    return B200PT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,212 @@
+// isect.h - ray/box and ray/triangle arithmetic, operation for operation as the
+// reference evaluates it, so that hit t / barycentrics are bit-identical to
+// BVHAggregate::Intersect on the CPU (BASELINE.json north_star).
+//
+//   SlabTest        = Bounds3::IntersectP(o,d,tMax,invDir,dirIsNeg)  util/vecmath.h:1576-1610
+//   TriSetup/TriHit = IntersectTriangle                              shapes.cpp:172-273
+//   DiffOfProducts  = DifferenceOfProducts                           util/math.h:569-575
+//
+// Every multiply/add goes through rn-intrinsics on the device (never contracted
+// into FMA by ptxas, whatever --fmad says); FMA appears only where the
+// reference calls FMA().  The same header compiles for the host (g++
+// -ffp-contract=off) so tests can run this exact arithmetic against the
+// compiled reference without a GPU (tests/native/hostcheck.cpp).
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#if defined(__CUDA_ARCH__)
+#define B2_HD __host__ __device__ __forceinline__
+#define B2_MUL(a, b) __fmul_rn((a), (b))
+#define B2_ADD(a, b) __fadd_rn((a), (b))
+#define B2_SUB(a, b) __fsub_rn((a), (b))
+#define B2_DIV(a, b) __fdiv_rn((a), (b))
+#define B2_FMA(a, b, c) __fmaf_rn((a), (b), (c))
+#define B2_DMUL(a, b) __dmul_rn((a), (b))
+#define B2_DSUB(a, b) __dsub_rn((a), (b))
+#define B2_D2F(a) __double2float_rn(a)
+#else
+#if defined(__CUDACC__)
+#define B2_HD __host__ __device__ inline
+#else
+#define B2_HD inline
+#endif
+#define B2_MUL(a, b) ((a) * (b))
+#define B2_ADD(a, b) ((a) + (b))
+#define B2_SUB(a, b) ((a) - (b))
+#define B2_DIV(a, b) ((a) / (b))
+#define B2_FMA(a, b, c) __builtin_fmaf((a), (b), (c))
+#define B2_DMUL(a, b) ((a) * (b))
+#define B2_DSUB(a, b) ((a) - (b))
+#define B2_D2F(a) ((float)(a))
+#endif
+
+namespace b200pt {
+
+// gamma(n) = n*eps/(1 - n*eps), eps = 2^-24 (util/float.h:45,197-199), in float.
+B2_HD constexpr float GammaF(int n) {
+    return (n * 5.9604644775390625e-08f) / (1 - n * 5.9604644775390625e-08f);
+}
+// 1 + 2*gamma(3) as the reference's float expression (util/vecmath.h:1588)
+constexpr float kSlabPad = 1 + 2 * GammaF(3);
+
+B2_HD float DiffOfProducts(float a, float b, float c, float d) {
+    float cd = B2_MUL(c, d);
+    float dop = B2_FMA(a, b, -cd);
+    float err = B2_FMA(-c, d, cd);
+    return B2_ADD(dop, err);
+}
+
+struct RayCtx {
+    float ox, oy, oz;
+    float dx, dy, dz;
+    float ix, iy, iz;  // 1/d (cpu/aggregates.cpp:534)
+    int neg[3];        // invDir < 0
+    // IntersectTriangle's per-ray shear terms (shapes.cpp:186-204); they depend
+    // on the ray only, so they are hoisted out of the per-triangle work.
+    int kx, ky, kz;
+    float Sx, Sy, Sz;
+};
+
+B2_HD float Comp(float x, float y, float z, int k) {
+    return k == 0 ? x : (k == 1 ? y : z);
+}
+
+B2_HD void RaySetup(RayCtx &r, float ox, float oy, float oz, float dx, float dy, float dz) {
+    r.ox = ox; r.oy = oy; r.oz = oz;
+    r.dx = dx; r.dy = dy; r.dz = dz;
+    r.ix = B2_DIV(1.f, dx);
+    r.iy = B2_DIV(1.f, dy);
+    r.iz = B2_DIV(1.f, dz);
+    r.neg[0] = r.ix < 0;
+    r.neg[1] = r.iy < 0;
+    r.neg[2] = r.iz < 0;
+    // MaxComponentIndex(Abs(d)) (util/vecmath.h:456-458)
+    float ax = fabsf(dx), ay = fabsf(dy), az = fabsf(dz);
+    int kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
+    int kx = kz + 1;
+    if (kx == 3) kx = 0;
+    int ky = kx + 1;
+    if (ky == 3) ky = 0;
+    r.kx = kx; r.ky = ky; r.kz = kz;
+    float pdx = Comp(dx, dy, dz, kx), pdy = Comp(dx, dy, dz, ky), pdz = Comp(dx, dy, dz, kz);
+    r.Sx = B2_DIV(-pdx, pdz);
+    r.Sy = B2_DIV(-pdy, pdz);
+    r.Sz = B2_DIV(1.f, pdz);
+}
+
+// Bounds3::IntersectP with precomputed invDir/dirIsNeg.
+B2_HD bool SlabTest(const RayCtx &r, const float *bmin, const float *bmax, float raytMax) {
+    float tMin = B2_MUL(B2_SUB((r.neg[0] ? bmax[0] : bmin[0]), r.ox), r.ix);
+    float tMax = B2_MUL(B2_SUB((r.neg[0] ? bmin[0] : bmax[0]), r.ox), r.ix);
+    float tyMin = B2_MUL(B2_SUB((r.neg[1] ? bmax[1] : bmin[1]), r.oy), r.iy);
+    float tyMax = B2_MUL(B2_SUB((r.neg[1] ? bmin[1] : bmax[1]), r.oy), r.iy);
+    tMax = B2_MUL(tMax, kSlabPad);
+    tyMax = B2_MUL(tyMax, kSlabPad);
+    if (tMin > tyMax || tyMin > tMax)
+        return false;
+    if (tyMin > tMin) tMin = tyMin;
+    if (tyMax < tMax) tMax = tyMax;
+    float tzMin = B2_MUL(B2_SUB((r.neg[2] ? bmax[2] : bmin[2]), r.oz), r.iz);
+    float tzMax = B2_MUL(B2_SUB((r.neg[2] ? bmin[2] : bmax[2]), r.oz), r.iz);
+    tzMax = B2_MUL(tzMax, kSlabPad);
+    if (tMin > tzMax || tzMin > tMax)
+        return false;
+    if (tzMin > tMin) tMin = tzMin;
+    if (tzMax < tMax) tMax = tzMax;
+    return (tMin < raytMax) && (tMax > 0);
+}
+
+B2_HD float Max3Abs(float a, float b, float c) {
+    // MaxComponentValue(Abs(v)) = std::max({|a|,|b|,|c|}) (util/vecmath.h:450-453)
+    float m = fabsf(a);
+    float fb = fabsf(b), fc = fabsf(c);
+    if (m < fb) m = fb;
+    if (m < fc) m = fc;
+    return m;
+}
+
+// IntersectTriangle (shapes.cpp:172-273).  Returns true and fills t,b0,b1,b2 on a hit
+// with t in (deltaT, tMax].
+B2_HD bool TriHit(const RayCtx &r, float tMax, const float *p0, const float *p1, const float *p2,
+                  float &tOut, float &b0Out, float &b1Out, float &b2Out) {
+    // degenerate: LengthSquared(Cross(p2 - p0, p1 - p0)) == 0
+    {
+        float ax = B2_SUB(p2[0], p0[0]), ay = B2_SUB(p2[1], p0[1]), az = B2_SUB(p2[2], p0[2]);
+        float bx = B2_SUB(p1[0], p0[0]), by = B2_SUB(p1[1], p0[1]), bz = B2_SUB(p1[2], p0[2]);
+        float cx = DiffOfProducts(ay, bz, az, by);
+        float cy = DiffOfProducts(az, bx, ax, bz);
+        float cz = DiffOfProducts(ax, by, ay, bx);
+        float l2 = B2_ADD(B2_ADD(B2_MUL(cx, cx), B2_MUL(cy, cy)), B2_MUL(cz, cz));
+        if (l2 == 0)
+            return false;
+    }
+    // translate, permute
+    float t0x = B2_SUB(p0[0], r.ox), t0y = B2_SUB(p0[1], r.oy), t0z = B2_SUB(p0[2], r.oz);
+    float t1x = B2_SUB(p1[0], r.ox), t1y = B2_SUB(p1[1], r.oy), t1z = B2_SUB(p1[2], r.oz);
+    float t2x = B2_SUB(p2[0], r.ox), t2y = B2_SUB(p2[1], r.oy), t2z = B2_SUB(p2[2], r.oz);
+    float p0x = Comp(t0x, t0y, t0z, r.kx), p0y = Comp(t0x, t0y, t0z, r.ky), p0z = Comp(t0x, t0y, t0z, r.kz);
+    float p1x = Comp(t1x, t1y, t1z, r.kx), p1y = Comp(t1x, t1y, t1z, r.ky), p1z = Comp(t1x, t1y, t1z, r.kz);
+    float p2x = Comp(t2x, t2y, t2z, r.kx), p2y = Comp(t2x, t2y, t2z, r.ky), p2z = Comp(t2x, t2y, t2z, r.kz);
+    // shear (p.x += Sx * p.z: a multiply then an add, not fused)
+    p0x = B2_ADD(p0x, B2_MUL(r.Sx, p0z));
+    p0y = B2_ADD(p0y, B2_MUL(r.Sy, p0z));
+    p1x = B2_ADD(p1x, B2_MUL(r.Sx, p1z));
+    p1y = B2_ADD(p1y, B2_MUL(r.Sy, p1z));
+    p2x = B2_ADD(p2x, B2_MUL(r.Sx, p2z));
+    p2y = B2_ADD(p2y, B2_MUL(r.Sy, p2z));
+    // edge functions
+    float e0 = DiffOfProducts(p1x, p2y, p1y, p2x);
+    float e1 = DiffOfProducts(p2x, p0y, p2y, p0x);
+    float e2 = DiffOfProducts(p0x, p1y, p0y, p1x);
+    if (e0 == 0.0f || e1 == 0.0f || e2 == 0.0f) {
+        double p2txp1ty = B2_DMUL((double)p2x, (double)p1y);
+        double p2typ1tx = B2_DMUL((double)p2y, (double)p1x);
+        e0 = B2_D2F(B2_DSUB(p2typ1tx, p2txp1ty));
+        double p0txp2ty = B2_DMUL((double)p0x, (double)p2y);
+        double p0typ2tx = B2_DMUL((double)p0y, (double)p2x);
+        e1 = B2_D2F(B2_DSUB(p0typ2tx, p0txp2ty));
+        double p1txp0ty = B2_DMUL((double)p1x, (double)p0y);
+        double p1typ0tx = B2_DMUL((double)p1y, (double)p0x);
+        e2 = B2_D2F(B2_DSUB(p1typ0tx, p1txp0ty));
+    }
+    if ((e0 < 0 || e1 < 0 || e2 < 0) && (e0 > 0 || e1 > 0 || e2 > 0))
+        return false;
+    float det = B2_ADD(B2_ADD(e0, e1), e2);
+    if (det == 0)
+        return false;
+    p0z = B2_MUL(p0z, r.Sz);
+    p1z = B2_MUL(p1z, r.Sz);
+    p2z = B2_MUL(p2z, r.Sz);
+    float tScaled = B2_ADD(B2_ADD(B2_MUL(e0, p0z), B2_MUL(e1, p1z)), B2_MUL(e2, p2z));
+    if (det < 0 && (tScaled >= 0 || tScaled < B2_MUL(tMax, det)))
+        return false;
+    else if (det > 0 && (tScaled <= 0 || tScaled > B2_MUL(tMax, det)))
+        return false;
+    float invDet = B2_DIV(1.f, det);
+    float b0 = B2_MUL(e0, invDet), b1 = B2_MUL(e1, invDet), b2 = B2_MUL(e2, invDet);
+    float t = B2_MUL(tScaled, invDet);
+    // conservative t > 0 check
+    float maxZt = Max3Abs(p0z, p1z, p2z);
+    float deltaZ = B2_MUL(GammaF(3), maxZt);
+    float maxXt = Max3Abs(p0x, p1x, p2x);
+    float maxYt = Max3Abs(p0y, p1y, p2y);
+    float deltaX = B2_MUL(GammaF(5), B2_ADD(maxXt, maxZt));
+    float deltaY = B2_MUL(GammaF(5), B2_ADD(maxYt, maxZt));
+    float deltaE = B2_MUL(2.f, B2_ADD(B2_ADD(B2_MUL(B2_MUL(GammaF(2), maxXt), maxYt), B2_MUL(deltaY, maxXt)),
+                                     B2_MUL(deltaX, maxYt)));
+    float maxE = Max3Abs(e0, e1, e2);
+    float deltaT = B2_MUL(
+        B2_MUL(3.f, B2_ADD(B2_ADD(B2_MUL(B2_MUL(GammaF(3), maxE), maxZt), B2_MUL(deltaE, maxZt)),
+                           B2_MUL(deltaZ, maxE))),
+        fabsf(invDet));
+    if (t <= deltaT)
+        return false;
+    tOut = t;
+    b0Out = b0;
+    b1Out = b1;
+    b2Out = b2;
+    return true;
+}
+
+}  // namespace b200pt

@@ -1,0 +1,14 @@
+// kernels.h - launchers of the device kernels (one per .cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "device_scene.h"
+struct b200pt_hit;
+
+namespace b200pt {
+
+cudaError_t LaunchTraverseBVH2(const DeviceScene &sc, const float *rays, long long n, b200pt_hit *hits,
+                               unsigned char *occluded, bool any, unsigned long long *counters,
+                               int smCount, cudaStream_t stream);
+
+}  // namespace b200pt

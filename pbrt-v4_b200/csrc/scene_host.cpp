@@ -1,0 +1,205 @@
+// scene_host.cpp - scene description -> flat tables (see scene_host.h).
+#include "scene_host.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <map>
+
+namespace b200pt {
+namespace {
+
+// Triangle::Bounds = Union(Bounds3f(p0, p1), p2)  (reference shapes.cpp:294-301)
+inline Box TriBox(const float *p0, const float *p1, const float *p2) {
+    Box b;
+    for (int k = 0; k < 3; ++k) {
+        float lo = std::min(p0[k], p1[k]), hi = std::max(p0[k], p1[k]);
+        b.lo[k] = std::min(lo, p2[k]);
+        b.hi[k] = std::max(hi, p2[k]);
+    }
+    return b;
+}
+
+struct PrimRef {
+    uint32_t kind, a, b;
+};
+
+bool ValidateTree(const HostTree &t, uint32_t nPrims, std::string &err) {
+    const uint32_t nn = uint32_t(t.nodes.size());
+    if (nn == 0) {
+        err = "bvh with no nodes";
+        return false;
+    }
+    // every node reachable exactly once in DFS order, offsets in range
+    std::vector<uint32_t> stack{0};
+    uint32_t visited = 0;
+    while (!stack.empty()) {
+        uint32_t i = stack.back();
+        stack.pop_back();
+        if (i >= nn || ++visited > nn) {
+            err = "bvh node index out of range";
+            return false;
+        }
+        const Node32 &nd = t.nodes[i];
+        if (nd.nPrims > 0) {
+            if (nd.offset < 0 || uint64_t(nd.offset) + nd.nPrims > nPrims) {
+                err = "bvh leaf primitive range out of bounds";
+                return false;
+            }
+        } else {
+            if (nd.axis > 2 || nd.offset <= int32_t(i) || uint32_t(nd.offset) >= nn) {
+                err = "bvh interior node malformed";
+                return false;
+            }
+            stack.push_back(uint32_t(nd.offset));
+            stack.push_back(i + 1);
+        }
+    }
+    return true;
+}
+
+}  // namespace
+
+int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &err) {
+    auto t0 = std::chrono::steady_clock::now();
+    if (!desc || (desc->n_meshes && !desc->meshes) || (desc->n_instances && !desc->instances) ||
+        (desc->n_bvhs && !desc->bvhs)) {
+        err = "null scene description";
+        return B200PT_ERR_INVALID;
+    }
+    // ---- index the meshes by object; check indices
+    std::map<int32_t, std::vector<uint32_t>> objMeshes;  // object -> mesh ids, in array order
+    uint64_t nTri = 0;
+    for (uint32_t m = 0; m < desc->n_meshes; ++m) {
+        const b200pt_mesh &mesh = desc->meshes[m];
+        if ((mesh.n_vertices && !mesh.p) || (mesh.n_triangles && !mesh.indices)) {
+            err = "mesh with null arrays";
+            return B200PT_ERR_INVALID;
+        }
+        for (uint64_t i = 0; i < 3ull * mesh.n_triangles; ++i)
+            if (mesh.indices[i] < 0 || uint32_t(mesh.indices[i]) >= mesh.n_vertices) {
+                err = "vertex index out of range";
+                return B200PT_ERR_INVALID;
+            }
+        objMeshes[mesh.object < 0 ? -1 : mesh.object].push_back(m);
+        nTri += mesh.n_triangles;
+    }
+    out.nTriangles = nTri;
+    if (desc->n_instances) {
+        err = "instances are not supported by this build yet";
+        return B200PT_ERR_INVALID;
+    }
+    if (nTri == 0) {
+        err = "scene has no primitives";
+        return B200PT_ERR_INVALID;
+    }
+
+    // ---- trees: take the host's, or build with the reference's decisions
+    out.trees.clear();
+    if (desc->n_bvhs) {
+        for (uint32_t b = 0; b < desc->n_bvhs; ++b) {
+            const b200pt_bvh2 &src = desc->bvhs[b];
+            if (!src.nodes || !src.prims || !src.n_nodes) {
+                err = "bvh with null arrays";
+                return B200PT_ERR_INVALID;
+            }
+            HostTree t;
+            t.object = src.object < 0 ? -1 : src.object;
+            t.nodes.resize(src.n_nodes);
+            std::memcpy(t.nodes.data(), src.nodes, size_t(src.n_nodes) * 32);
+            t.prims.assign(src.prims, src.prims + 3ull * src.n_prims);
+            if (!ValidateTree(t, src.n_prims, err))
+                return B200PT_ERR_INVALID;
+            out.trees.push_back(std::move(t));
+        }
+        auto it = std::find_if(out.trees.begin(), out.trees.end(),
+                               [](const HostTree &t) { return t.object == -1; });
+        if (it == out.trees.end()) {
+            err = "no top-level bvh given";
+            return B200PT_ERR_INVALID;
+        }
+        std::iter_swap(it, out.trees.begin());  // top level first
+    } else {
+        // primitive order = the order the reference creates them in: meshes in
+        // array order, triangles in index order (shapes.cpp:284-289), world
+        // shapes before instances (scene.cpp:1447-1580).
+        for (auto &kv : objMeshes) {
+            if (kv.first == -1)
+                continue;
+            err = "object definitions are not supported by this build yet";
+            return B200PT_ERR_INVALID;
+        }
+        HostTree top;
+        top.object = -1;
+        std::vector<Box> boxes;
+        std::vector<PrimRef> refs;
+        for (uint32_t m : objMeshes[-1]) {
+            const b200pt_mesh &mesh = desc->meshes[m];
+            for (uint32_t i = 0; i < mesh.n_triangles; ++i) {
+                const int32_t *v = mesh.indices + 3ull * i;
+                boxes.push_back(TriBox(mesh.p + 3ull * v[0], mesh.p + 3ull * v[1], mesh.p + 3ull * v[2]));
+                refs.push_back({0, m, i});
+            }
+        }
+        std::vector<uint32_t> order;
+        BuildBVH2(boxes.data(), uint32_t(boxes.size()), 4, top.nodes, order);
+        top.prims.reserve(3 * order.size());
+        for (uint32_t id : order) {
+            top.prims.push_back(refs[id].kind);
+            top.prims.push_back(refs[id].a);
+            top.prims.push_back(refs[id].b);
+        }
+        out.trees.push_back(std::move(top));
+    }
+
+    // ---- flatten all trees into one node array + depth-first primitive slots
+    out.nodes.clear();
+    out.prims.clear();
+    out.treeRoot.clear();
+    for (const HostTree &t : out.trees) {
+        uint32_t base = uint32_t(out.nodes.size());
+        out.treeRoot.push_back(base);
+        for (size_t i = 0; i < t.nodes.size(); ++i) {
+            Node32 nd = t.nodes[i];
+            nd.pad = 0;
+            if (nd.nPrims == 0) {
+                nd.offset += int32_t(base);
+            } else {
+                nd.axis = 0;
+                uint32_t first = uint32_t(out.prims.size());
+                for (uint32_t k = 0; k < nd.nPrims; ++k) {
+                    const uint32_t *pr = &t.prims[3ull * (uint32_t(nd.offset) + k)];
+                    PrimSlot s;
+                    std::memset(&s, 0, sizeof s);
+                    if (pr[0] == 0) {
+                        if (pr[1] >= desc->n_meshes || pr[2] >= desc->meshes[pr[1]].n_triangles) {
+                            err = "bvh primitive refers to a missing triangle";
+                            return B200PT_ERR_INVALID;
+                        }
+                        const b200pt_mesh &mesh = desc->meshes[pr[1]];
+                        const int32_t *v = mesh.indices + 3ull * pr[2];
+                        std::memcpy(s.p0, mesh.p + 3ull * v[0], 12);
+                        std::memcpy(s.p1, mesh.p + 3ull * v[1], 12);
+                        std::memcpy(s.p2, mesh.p + 3ull * v[2], 12);
+                        s.mesh = pr[1];
+                        s.tri = pr[2];
+                    } else {
+                        err = "instance primitives are not supported by this build yet";
+                        return B200PT_ERR_INVALID;
+                    }
+                    out.prims.push_back(s);
+                }
+                nd.offset = int32_t(first);
+            }
+            out.nodes.push_back(nd);
+        }
+    }
+    out.rootNode = out.treeRoot[0];
+    const Node32 &root = out.nodes[out.rootNode];
+    std::memcpy(out.bounds, root.bmin, 12);
+    std::memcpy(out.bounds + 3, root.bmax, 12);
+    out.buildSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return B200PT_OK;
+}
+
+}  // namespace b200pt

@@ -1,0 +1,37 @@
+// scene_host.h - host-side flattening of a scene description into the POD
+// tables of device_scene.h.  Pure host code (no CUDA), compiled with
+// -ffp-contract=off because triangle bounds / SAH decisions must match the
+// reference float-for-float.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/b200pt.h"
+#include "bvh2.h"
+#include "device_scene.h"
+
+namespace b200pt {
+
+struct HostTree {
+    int32_t object = -1;
+    std::vector<Node32> nodes;       // offsets relative to this tree
+    std::vector<uint32_t> prims;     // 3 per ordered primitive {kind, a, b}
+};
+
+struct HostScene {
+    std::vector<HostTree> trees;     // [0] = top level
+    std::vector<Node32> nodes;       // all trees, absolute child / slot offsets
+    std::vector<PrimSlot> prims;
+    std::vector<InstanceDev> instances;
+    std::vector<uint32_t> treeRoot;  // root node of trees[i] in `nodes`
+    uint32_t rootNode = 0;
+    float bounds[6] = {0, 0, 0, 0, 0, 0};
+    uint64_t nTriangles = 0;
+    double buildSeconds = 0;
+};
+
+// Returns B200PT_OK or B200PT_ERR_INVALID (err filled).
+int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &err);
+
+}  // namespace b200pt

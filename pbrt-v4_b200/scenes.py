@@ -1,0 +1,243 @@
+"""Procedural scenes and ray batches for BASELINE.json's configs, plus
+the little-endian scene file (`.b2sc`) that carries the same geometry to both
+the product (through capi / B200Aggregate) and the reference driver
+(oracle/raycast_ref.cpp).  numpy only; nothing here computes intersections.
+
+File layout:  u32 magic 'B2SC', u32 version=1, u32 nMeshes, u32 nInstances
+  per mesh:     i32 object (-1 world), u32 nVerts, u32 nTris, f32 P[3nV], i32 idx[3nT]
+  per instance: u32 object, f32 renderFromInstance[16], f32 instanceFromRender[16]
+"""
+from dataclasses import dataclass, field
+from typing import List
+
+import numpy as np
+
+MAGIC = 0x43533242
+
+
+@dataclass
+class Mesh:
+    p: np.ndarray            # (nv, 3) float32, render space
+    indices: np.ndarray      # (nt, 3) int32
+    object: int = -1         # -1: world; >= 0: object definition id
+
+    def __post_init__(self):
+        self.p = np.ascontiguousarray(self.p, dtype=np.float32).reshape(-1, 3)
+        self.indices = np.ascontiguousarray(self.indices, dtype=np.int32).reshape(-1, 3)
+
+
+@dataclass
+class Instance:
+    object: int
+    render_from_instance: np.ndarray   # (4,4) float32
+    instance_from_render: np.ndarray   # (4,4) float32
+
+    def __post_init__(self):
+        self.render_from_instance = np.ascontiguousarray(self.render_from_instance, dtype=np.float32).reshape(4, 4)
+        self.instance_from_render = np.ascontiguousarray(self.instance_from_render, dtype=np.float32).reshape(4, 4)
+
+
+@dataclass
+class Scene:
+    meshes: List[Mesh] = field(default_factory=list)
+    instances: List[Instance] = field(default_factory=list)
+
+    @property
+    def n_triangles(self):
+        return sum(m.indices.shape[0] for m in self.meshes)
+
+    def write(self, path):
+        with open(path, "wb") as f:
+            np.array([MAGIC, 1, len(self.meshes), len(self.instances)], dtype="<u4").tofile(f)
+            for m in self.meshes:
+                np.array([m.object], dtype="<i4").tofile(f)
+                np.array([m.p.shape[0], m.indices.shape[0]], dtype="<u4").tofile(f)
+                m.p.astype("<f4").tofile(f)
+                m.indices.astype("<i4").tofile(f)
+            for i in self.instances:
+                np.array([i.object], dtype="<u4").tofile(f)
+                i.render_from_instance.astype("<f4").tofile(f)
+                i.instance_from_render.astype("<f4").tofile(f)
+
+    def triangle_vertices(self, mesh):
+        m = self.meshes[mesh]
+        return m.p[m.indices]  # (nt, 3, 3)
+
+    def triangle_boxes(self, meshes=None):
+        """(n,6) float32 boxes in reference primitive order (mesh order, then triangle order)."""
+        out = []
+        for k, m in enumerate(self.meshes):
+            if meshes is not None and k not in meshes:
+                continue
+            v = m.p[m.indices]
+            out.append(np.concatenate([v.min(axis=1), v.max(axis=1)], axis=1))
+        return np.concatenate(out, axis=0).astype(np.float32)
+
+
+# ------------------------------------------------------------------ scenes
+
+def random_soup(n_tris=1_000_000, seed=12111, s=0.01, n_meshes=1):
+    """BASELINE config 2: unit cube filled with random triangles: centre ~U[0,1]^3,
+    vertices = centre + U[-s,s]^3 (the construction of the reference's own
+    Triangle.Watertight test, shapes_test.cpp:33-60, scaled up)."""
+    rng = np.random.default_rng(seed)
+    meshes = []
+    per = [n_tris // n_meshes + (1 if i < n_tris % n_meshes else 0) for i in range(n_meshes)]
+    for cnt in per:
+        c = rng.random((cnt, 1, 3), dtype=np.float32)
+        v = (c + (rng.random((cnt, 3, 3), dtype=np.float32) * 2 - 1) * np.float32(s)).astype(np.float32)
+        meshes.append(Mesh(v.reshape(-1, 3), np.arange(3 * cnt, dtype=np.int32).reshape(-1, 3)))
+    return Scene(meshes)
+
+
+def _quad(p0, p1, p2, p3):
+    return Mesh(np.array([p0, p1, p2, p3], dtype=np.float32), np.array([[0, 1, 2], [0, 2, 3]], dtype=np.int32))
+
+
+def _box(lo, hi, rot_y=0.0, centre=None):
+    lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+    c = np.array([[lo[0], lo[1], lo[2]], [hi[0], lo[1], lo[2]], [hi[0], hi[1], lo[2]], [lo[0], hi[1], lo[2]],
+                  [lo[0], lo[1], hi[2]], [hi[0], lo[1], hi[2]], [hi[0], hi[1], hi[2]], [lo[0], hi[1], hi[2]]])
+    if rot_y:
+        ctr = (lo + hi) / 2 if centre is None else np.asarray(centre, np.float64)
+        ca, sa = np.cos(rot_y), np.sin(rot_y)
+        R = np.array([[ca, 0, sa], [0, 1, 0], [-sa, 0, ca]])
+        c = (c - ctr) @ R.T + ctr
+    quads = [[0, 3, 2, 1], [4, 5, 6, 7], [0, 1, 5, 4], [2, 3, 7, 6], [1, 2, 6, 5], [0, 4, 7, 3]]
+    idx = []
+    for q in quads:
+        idx += [[q[0], q[1], q[2]], [q[0], q[2], q[3]]]
+    return Mesh(c.astype(np.float32), np.array(idx, dtype=np.int32))
+
+
+def cornell_box():
+    """BASELINE config 1 geometry: 5 wall quads, a ceiling light quad and 2 boxes
+    (axis-aligned walls make exact t ties along shared diagonals - the tie-breaking
+    case of SURVEY F7)."""
+    m = [
+        _quad([0, 0, 0], [1, 0, 0], [1, 0, 1], [0, 0, 1]),      # floor
+        _quad([0, 1, 0], [0, 1, 1], [1, 1, 1], [1, 1, 0]),      # ceiling
+        _quad([0, 0, 1], [1, 0, 1], [1, 1, 1], [0, 1, 1]),      # back
+        _quad([0, 0, 0], [0, 0, 1], [0, 1, 1], [0, 1, 0]),      # left (red)
+        _quad([1, 0, 0], [1, 1, 0], [1, 1, 1], [1, 0, 1]),      # right (green)
+        _quad([0.35, 0.999, 0.35], [0.65, 0.999, 0.35], [0.65, 0.999, 0.65], [0.35, 0.999, 0.65]),  # light
+        _box([0.15, 0, 0.5], [0.45, 0.6, 0.8], rot_y=0.3),      # tall box
+        _box([0.55, 0, 0.2], [0.85, 0.3, 0.5], rot_y=-0.3),     # short box
+    ]
+    return Scene(m)
+
+
+def grid_sheet(nx=64, ny=64, z=0.5, jitter=0.0, seed=1):
+    """Indexed mesh with shared vertices/edges (watertightness + tie cases)."""
+    rng = np.random.default_rng(seed)
+    xs, ys = np.meshgrid(np.linspace(0, 1, nx + 1), np.linspace(0, 1, ny + 1), indexing="ij")
+    zs = np.full_like(xs, z) + (rng.random(xs.shape) * 2 - 1) * jitter
+    p = np.stack([xs, ys, zs], axis=-1).reshape(-1, 3).astype(np.float32)
+    idx = []
+    for i in range(nx):
+        for j in range(ny):
+            a, b, c, d = i * (ny + 1) + j, (i + 1) * (ny + 1) + j, (i + 1) * (ny + 1) + j + 1, i * (ny + 1) + j + 1
+            idx += [[a, b, c], [a, c, d]]
+    return Mesh(p, np.array(idx, dtype=np.int32))
+
+
+# ------------------------------------------------------------------ ray batches
+# rays: (n,7) float32 rows {o.xyz, d.xyz, tMax}
+
+def _unit_sphere(rng, n):
+    z = 1 - 2 * rng.random(n)
+    r = np.sqrt(np.maximum(0, 1 - z * z))
+    phi = 2 * np.pi * rng.random(n)
+    return np.stack([r * np.cos(phi), r * np.sin(phi), z], axis=1)
+
+
+def primary_rays(n, seed=1, centre=(0.5, 0.5, 0.5), radius=2.0, lo=0.1, hi=0.9):
+    """Origins on a sphere about the cube, aimed at uniform points in [lo,hi]^3, tMax = inf
+    (SURVEY 8d config 2)."""
+    rng = np.random.default_rng(seed)
+    o = np.asarray(centre) + radius * _unit_sphere(rng, n)
+    tgt = lo + (hi - lo) * rng.random((n, 3))
+    d = tgt - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.empty((n, 7), dtype=np.float32)
+    rays[:, 0:3], rays[:, 3:6], rays[:, 6] = o, d, np.inf
+    return rays
+
+
+def shadow_rays(rays, hits, seed=2, light_lo=(0, 1.0, 0), light_hi=(1, 1.0, 1)):
+    """From each primary hit point (offset 1e-3 back along the ray) to a uniform point on the
+    cube's top face: d unnormalised, tMax = 1 - ShadowEpsilon (cpu/integrators.cpp:297-314,
+    ray.h:95-109).  Misses shoot from the origin of the primary ray."""
+    rng = np.random.default_rng(seed)
+    n = rays.shape[0]
+    t = np.where(hits["mesh"] != 0xFFFFFFFF, hits["t"], 0).astype(np.float64)
+    o = rays[:, 0:3].astype(np.float64) + rays[:, 3:6].astype(np.float64) * (t - 1e-3)[:, None]
+    l0, l1 = np.asarray(light_lo, np.float64), np.asarray(light_hi, np.float64)
+    tgt = l0 + (l1 - l0) * rng.random((n, 3))
+    out = np.empty((n, 7), dtype=np.float32)
+    out[:, 0:3] = o
+    out[:, 3:6] = tgt - o
+    out[:, 6] = np.float32(1 - 1e-4)
+    return out
+
+
+def adversarial_rays(scene, n, seed=3):
+    """Rays that stress tie-breaking and NaN/inf paths: through mesh vertices, through edge
+    midpoints, along +-axes (zero direction components -> invDir = +-inf), and from origins
+    lying exactly in bounding planes."""
+    rng = np.random.default_rng(seed)
+    verts = np.concatenate([m.p[m.indices].reshape(-1, 3) for m in scene.meshes if m.object < 0], axis=0)
+    tris = np.concatenate([m.p[m.indices] for m in scene.meshes if m.object < 0], axis=0)
+    k = n // 4
+    rays = np.empty((4 * k, 7), dtype=np.float32)
+    # 1) through vertices from random outside origins
+    o = 0.5 + 2.0 * _unit_sphere(rng, k)
+    v = verts[rng.integers(0, verts.shape[0], k)]
+    rays[0:k, 0:3], rays[0:k, 3:6] = o, v - o
+    # 2) through edge midpoints
+    t = tris[rng.integers(0, tris.shape[0], k)]
+    e = rng.integers(0, 3, k)
+    mid = 0.5 * (t[np.arange(k), e] + t[np.arange(k), (e + 1) % 3])
+    o = 0.5 + 2.0 * _unit_sphere(rng, k)
+    rays[k:2 * k, 0:3], rays[k:2 * k, 3:6] = o, mid - o
+    # 3) axis-aligned rays through vertices (two zero components in d)
+    ax = rng.integers(0, 3, k)
+    sgn = rng.choice([-1.0, 1.0], k)
+    v = verts[rng.integers(0, verts.shape[0], k)].astype(np.float64)
+    d = np.zeros((k, 3))
+    d[np.arange(k), ax] = sgn
+    o = v - 3.0 * d
+    rays[2 * k:3 * k, 0:3], rays[2 * k:3 * k, 3:6] = o, d
+    # 4) one zero component, origin sharing a coordinate with a vertex (in-plane rays)
+    v = verts[rng.integers(0, verts.shape[0], k)].astype(np.float64)
+    ax = rng.integers(0, 3, k)
+    d = _unit_sphere(rng, k)
+    d[np.arange(k), ax] = 0.0
+    d[np.arange(k), (ax + 1) % 3] += 1e-3
+    o = v - 2.5 * d
+    rays[3 * k:, 0:3], rays[3 * k:, 3:6] = o, d
+    rays[:, 6] = np.inf
+    return rays
+
+
+def camera_rays(width, height, eye, look, up=(0, 1, 0), fov_deg=40.0, spp=1, seed=0):
+    """Simple pinhole batch (pixel centres or jittered) for config-1 style parity batches."""
+    rng = np.random.default_rng(seed)
+    eye, look, up = (np.asarray(a, np.float64) for a in (eye, look, up))
+    w = look - eye
+    w /= np.linalg.norm(w)
+    u = np.cross(up, w)
+    u /= np.linalg.norm(u)
+    v = np.cross(w, u)
+    ys, xs = np.meshgrid(np.arange(height), np.arange(width), indexing="ij")
+    xs = np.repeat(xs.reshape(-1), spp).astype(np.float64)
+    ys = np.repeat(ys.reshape(-1), spp).astype(np.float64)
+    jx, jy = (rng.random(xs.shape), rng.random(xs.shape)) if spp > 1 else (0.5, 0.5)
+    s = np.tan(np.radians(fov_deg) / 2)
+    px = (2 * (xs + jx) / width - 1) * s * (width / height)
+    py = (1 - 2 * (ys + jy) / height) * s
+    d = px[:, None] * u + py[:, None] * v + w
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.empty((xs.shape[0], 7), dtype=np.float32)
+    rays[:, 0:3], rays[:, 3:6], rays[:, 6] = eye, d, np.inf
+    return rays
