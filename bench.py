@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py - BASELINE.json's metric on its config 2: Mrays/s of BVH traversal
+(closest-hit + shadow any-hit) over the procedural 1M-triangle scene.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One "step" = one pass of the hot path over one batch: `--rays` primary rays through
+b200pt_intersect_closest plus as many shadow rays through b200pt_intersect_any.
+`value` times the kernels with the batches resident in HBM; `e2e` times the same
+calls through the C ABI with pinned HOST buffers (H2D + kernels + D2H inside the timed
+region).  Under torchrun every rank traces its own full batch against a replicated scene
+(weak scaling, no data-path collective); time = max over ranks.
+`--impl reference` times the reference's own CPU BVHAggregate (oracle/_ref/raycast_ref)
+on a bounded sample of the same batches, on all host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "traversal_mrays_per_s"
+UNIT = "Mrays/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tris", type=int, default=1_000_000)
+    ap.add_argument("--rays", type=int, default=1 << 24, help="primary rays per step (as many shadow rays)")
+    ap.add_argument("--cpu-sample", type=int, default=1 << 21, help="rays of each kind in the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args):
+    return {"workload": f"config2: procedural {args.tris}-triangle random-mesh scene (seed 12111), "
+                        f"{args.rays} primary closest-hit + {args.rays} shadow any-hit rays per step",
+            "triangles": args.tris, "rays_per_step": 2 * args.rays,
+            "l2_policy": "ray/hit buffers (28+24 B/ray x %d rays) exceed the 126 MB L2; no flush needed" % args.rays,
+            "parallelism": "rays sharded by rank, scene replicated"}
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if not self.proc:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1]))
+                mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.path)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+def make_batches(P, agg, n, seed):
+    prim = P.scenes.primary_rays(n, seed=seed)
+    hits = np.empty(n, dtype=P.capi.HIT_DTYPE)
+    chunk = 1 << 22
+    for a in range(0, n, chunk):
+        hits[a:a + chunk] = agg.IntersectClosest(prim[a:a + chunk])
+    shad = P.scenes.shadow_rays(prim, hits, seed=seed + 1000)
+    return prim, shad
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU BVHAggregate on all host cores, bounded sample per step."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refrun
+    import pbrt_v4_b200 as P
+    n = min(args.rays, args.cpu_sample)
+    sc = P.scenes.random_soup(args.tris, seed=12111)
+    prim = P.scenes.primary_rays(n, seed=1)
+    rs = refrun.RefScene(sc)
+    hits, info0 = rs.closest(prim)  # also the first warm-up; gives shadow origins
+    gold = np.zeros(n, dtype=P.capi.HIT_DTYPE)
+    gold["mesh"], gold["t"] = hits["mesh"], hits["t"]
+    shad = P.scenes.shadow_rays(prim, gold, seed=1001)
+    # raycast_ref repeats the batch `reps` times inside one process and reports the best pass;
+    # we want K timed steps after W warm-ups: run reps = W + K and use per-pass best as the step time
+    # (the tree build, ~1 s, is outside the timer as for the GPU arm).
+    reps = args.warmup + args.steps
+    _, ic = rs.closest(prim, nthreads=0, reps=reps)
+    _, ia = rs.any(shad, nthreads=0, reps=reps)
+    sec = ic["seconds"] + ia["seconds"]
+    val = 2 * n / sec * 1e-6
+    cores = ic["threads"]
+    line = {"metric": METRIC, "value": val, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args),
+            "closest_mrays_per_s": ic["mrays_per_s"], "any_mrays_per_s": ia["mrays_per_s"],
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "reference",
+                             "sample": f"{n} primary + {n} shadow rays of the same workload, best of "
+                                       f"{reps} passes, BVH build excluded ({ic['build_s']:.2f} s)"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    import torch
+    import pbrt_v4_b200 as P
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the b200pt path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- scene (replicated) and this rank's batches
+    sc = P.scenes.random_soup(args.tris, seed=12111)
+    stream = torch.cuda.current_stream()
+    agg = P.B200Aggregate(sc, device=local, stream=stream.cuda_stream)
+    st = agg.stats()
+    n = args.rays
+    prim, shad = make_batches(P, agg, n, seed=1 + rank)
+
+    # algorithmic bytes per ray from the counting variant (outside the timed region)
+    sample = slice(0, min(n, 1 << 22))
+    agg.IntersectClosest(prim[sample], counters=True)
+    tc = agg.trace_stats()
+    agg.IntersectShadow(shad[sample], counters=True)
+    ta = agg.trace_stats()
+    NODE_B, PRIM_B = 32, 48
+    bytes_closest = 28 + 24 + (NODE_B * tc["nodes_visited"] + PRIM_B * tc["prims_tested"]) / tc["rays"]
+    bytes_any = 28 + 1 + (NODE_B * ta["nodes_visited"] + PRIM_B * ta["prims_tested"]) / ta["rays"]
+
+    # ---- device-resident timing (value)
+    d_prim = torch.from_numpy(prim).cuda()
+    d_shad = torch.from_numpy(shad).cuda()
+    d_hits = torch.empty(n * 24, dtype=torch.uint8, device="cuda")
+    d_occ = torch.empty(n, dtype=torch.uint8, device="cuda")
+
+    def step_device():
+        agg.intersect_closest_ptr(d_prim.data_ptr(), n, d_hits.data_ptr(), P.capi.MEM_DEVICE)
+        agg.intersect_any_ptr(d_shad.data_ptr(), n, d_occ.data_ptr(), P.capi.MEM_DEVICE)
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3 * args.steps + 1)]
+    ev[0].record(stream)
+    for k in range(args.steps):
+        agg.intersect_closest_ptr(d_prim.data_ptr(), n, d_hits.data_ptr(), P.capi.MEM_DEVICE)
+        ev[3 * k + 1].record(stream)
+        agg.intersect_any_ptr(d_shad.data_ptr(), n, d_occ.data_ptr(), P.capi.MEM_DEVICE)
+        ev[3 * k + 2].record(stream)
+        ev[3 * k + 3].record(stream)
+    barrier()
+    total_ms = ev[0].elapsed_time(ev[3 * args.steps])
+    ms_closest = float(np.mean([ev[3 * k].elapsed_time(ev[3 * k + 1]) for k in range(args.steps)]))
+    ms_any = float(np.mean([ev[3 * k + 1].elapsed_time(ev[3 * k + 2]) for k in range(args.steps)]))
+    clk = clocks.stop() if rank == 0 else None
+
+    # ---- end to end through the C ABI with pinned host buffers (e2e)
+    h_prim = torch.from_numpy(prim).pin_memory()
+    h_shad = torch.from_numpy(shad).pin_memory()
+    h_hits = torch.empty(n * 24, dtype=torch.uint8).pin_memory()
+    h_occ = torch.empty(n, dtype=torch.uint8).pin_memory()
+
+    def step_host():
+        agg.intersect_closest_ptr(h_prim.data_ptr(), n, h_hits.data_ptr(), P.capi.MEM_HOST)
+        agg.intersect_any_ptr(h_shad.data_ptr(), n, h_occ.data_ptr(), P.capi.MEM_HOST)
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    # the e2e result really is the device result
+    if rank == 0:
+        assert np.array_equal(h_hits.numpy(), d_hits.cpu().numpy()) and np.array_equal(h_occ.numpy(), d_occ.cpu().numpy())
+
+    # ---- max over ranks
+    t = torch.tensor([total_ms, e2e_s, ms_closest, ms_any], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_s, ms_closest, ms_any = (float(x) for x in t.cpu())
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        rays_total = 2.0 * n * world * args.steps
+        value = rays_total / (total_ms * 1e-3) * 1e-6
+        ach = bytes_closest * n / (ms_closest * 1e-3) * 1e-9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args),
+            "closest_mrays_per_s": n * world / (ms_closest * 1e-3) * 1e-6,
+            "any_mrays_per_s": n * world / (ms_any * 1e-3) * 1e-6,
+            "roofline": {"bound": "hbm", "kernel": "closest-hit traversal", "achieved": ach, "peak": peak,
+                         "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "bytes_per_ray": bytes_closest, "bytes_per_ray_any": bytes_any,
+                         "nodes_per_ray": tc["nodes_visited"] / tc["rays"],
+                         "prims_per_ray": tc["prims_tested"] / tc["rays"],
+                         "compulsory_bytes_per_ray": 52},
+            "e2e": {"value": rays_total / e2e_s * 1e-6, "unit": UNIT,
+                    "h2d_bytes_per_step": 2 * n * 28, "d2h_bytes_per_step": n * 24 + n},
+            "gpu_launches": 2 * args.steps,
+            "clocks": clk,
+            "scene": {"bvh2_nodes": st["n_bvh2_nodes"], "wide_nodes": st["n_wide_nodes"],
+                      "device_bytes": st["device_bytes"], "build_s": st["build_seconds"]},
+        }
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args, P, sc, prim, shad)
+        print(json.dumps(line), flush=True)
+    agg.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args, P, sc, prim, shad):
+    """The reference's own BVHAggregate (oracle/_ref/raycast_ref) on a bounded sample, all host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refrun
+    if not refrun.available():
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    m = min(args.cpu_sample, prim.shape[0])
+    rs = refrun.RefScene(sc)
+    _, ic = rs.closest(prim[:m], nthreads=0, reps=2)
+    _, ia = rs.any(shad[:m], nthreads=0, reps=2)
+    sec = ic["seconds"] + ia["seconds"]
+    return {"value": 2 * m / sec * 1e-6, "unit": UNIT, "cores": ic["threads"], "kind": "reference",
+            "closest_mrays_per_s": ic["mrays_per_s"], "any_mrays_per_s": ia["mrays_per_s"],
+            "sample": f"first {m} primary + {m} shadow rays of the timed batches, best of 2 passes, "
+                      f"BVH build excluded ({ic['build_s']:.2f} s)"}
+
+
+if __name__ == "__main__":
+    main()

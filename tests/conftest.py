@@ -1,0 +1,60 @@
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def P():
+    import pbrt_v4_b200 as pkg
+    if not os.path.exists(pkg.capi.LIB_PATH):
+        pkg.build()
+    return pkg
+
+
+@pytest.fixture(scope="session")
+def refrun():
+    import refrun as r
+    if not r.available():
+        pytest.skip("oracle/_ref/raycast_ref not built (needs /root/reference: make -f oracle/ref.mk)")
+    return r
+
+
+@pytest.fixture(scope="session")
+def hostcheck_bin():
+    """TEST-ONLY host build of the device arithmetic (tests/native/hostcheck.cpp)."""
+    out = os.path.join(ROOT, "tests", "native", "_build", "hostcheck")
+    src = [os.path.join(ROOT, "tests", "native", "hostcheck.cpp"),
+           os.path.join(ROOT, "pbrt-v4_b200", "csrc", "scene_host.cpp"),
+           os.path.join(ROOT, "pbrt-v4_b200", "csrc", "bvh2_build.cpp")]
+    deps = src + [os.path.join(ROOT, "pbrt-v4_b200", "csrc", h) for h in ("isect.h", "scene_host.h", "bvh2.h")]
+    if not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-march=x86-64-v3", "-o", out] + src)
+    return out
+
+
+def hit_mismatches(mine, ref):
+    """Bit-exact comparison of product hits (capi.HIT_DTYPE) with reference hits
+    (refrun.REF_HIT_DTYPE).  ids and t by bits; barycentrics through the reference's uv
+    (default uv (0,0),(1,0),(1,1): u = b1 + b2, v = b2; `+ 0.0` folds -0, which the
+    reference's b0*0 + ... sum also does, shapes.h:884-1010)."""
+    hit = ref["mesh"] != 0xFFFFFFFF
+    z = np.float32(0.0)
+    bad = mine["mesh"] != ref["mesh"]
+    bad |= hit & (mine["prim"] != ref["prim"])
+    bad |= hit & (mine["instance"] != ref["instance"])
+    bad |= hit & (mine["t"].view("u4") != ref["t"].view("u4"))
+    bad |= hit & ((mine["b2"] + z).view("u4") != (ref["uv"][:, 1] + z).view("u4"))
+    bad |= hit & (((mine["b1"] + mine["b2"]).astype("f4") + z).view("u4") != (ref["uv"][:, 0] + z).view("u4"))
+    return bad

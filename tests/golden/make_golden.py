@@ -1,0 +1,60 @@
+"""Regenerates tests/golden/*.npz from the compiled reference (oracle/_ref/raycast_ref).
+Run in the build container (needs /root/reference -> `make -f oracle/ref.mk`):
+    python tests/golden/make_golden.py
+Each fixture stores the ray batch and the reference's BVHAggregate::Intersect / IntersectP
+answers for a scene that tests re-create from the same seeds (cases() below)."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+def cases(S):
+    soup = S.random_soup(20000, seed=21, n_meshes=2)
+    cb = S.cornell_box()
+    sheet = S.Scene([S.grid_sheet(32, 32, jitter=0.0), S.grid_sheet(24, 24, z=0.75, jitter=0.02, seed=9)])
+    return {
+        "soup20k_primary": (soup, S.primary_rays(40000, seed=31)),
+        "soup20k_adversarial": (soup, S.adversarial_rays(soup, 20000, seed=32)),
+        "cornell_camera": (cb, S.camera_rays(128, 128, (0.5, 0.5, -1.4), (0.5, 0.5, 0.5), spp=1)),
+        "cornell_adversarial": (cb, S.adversarial_rays(cb, 20000, seed=33)),
+        "sheets_adversarial": (sheet, S.adversarial_rays(sheet, 20000, seed=34)),
+    }
+
+
+GOLD_DTYPE = np.dtype([("mesh", "<u4"), ("prim", "<u4"), ("instance", "<u4"), ("t", "<f4"), ("uv", "<f4", 2)])
+
+
+def compact(h):
+    out = np.zeros(h.shape[0], dtype=GOLD_DTYPE)
+    for f in GOLD_DTYPE.names:
+        out[f] = h[f]
+    return out
+
+
+def load(name):
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), name + ".npz"))
+    n = z["hits"].shape[0]
+    return {"hits": z["hits"], "occ": np.unpackbits(z["occ"])[:n], "shadow_hits": z["shadow_hits"],
+            "shadow_occ": np.unpackbits(z["shadow_occ"])[:n]}
+
+
+if __name__ == "__main__":
+    import pbrt_v4_b200 as P
+    import refrun
+    out = os.path.dirname(os.path.abspath(__file__))
+    for name, (sc, rays) in cases(P.scenes).items():
+        rs = refrun.RefScene(sc)
+        hits, _ = rs.closest(rays)
+        occ, _ = rs.any(rays)
+        sh = P.scenes.shadow_rays(rays, hits, seed=35)
+        hits_sh, _ = rs.closest(sh)
+        occ_sh, _ = rs.any(sh)
+        # rays are re-created from the seeds by the tests; only the answers are stored
+        np.savez_compressed(os.path.join(out, name + ".npz"), hits=compact(hits), occ=np.packbits(occ),
+                            shadow_hits=compact(hits_sh), shadow_occ=np.packbits(occ_sh))
+        print(name, len(rays), "hit", (hits["mesh"] != 0xFFFFFFFF).mean(), "occluded(shadow)", occ_sh.mean())

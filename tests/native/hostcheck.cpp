@@ -1,0 +1,93 @@
+// tests/native/hostcheck.cpp - TEST-ONLY host build of the device arithmetic in
+// pbrt-v4_b200/csrc/isect.h, driving the same depth-first binary traversal as
+// traverse_bvh2.cu on the CPU, so the restated slab / triangle arithmetic can be
+// compared bit-for-bit with the compiled reference in the GPU-less container.
+// It is not part of libb200pt.so and nothing in the product calls it.
+//   hostcheck scene.b2sc rays.f32 {closest|any} out.bin
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../pbrt-v4_b200/csrc/isect.h"
+#include "../../pbrt-v4_b200/csrc/scene_host.h"
+
+using namespace b200pt;
+
+int main(int argc, char **argv) {
+    if (argc < 5) return 2;
+    FILE *f = fopen(argv[1], "rb");
+    uint32_t hdr[4];
+    if (!f || fread(hdr, 4, 4, f) != 4) return 2;
+    std::vector<std::vector<float>> P(hdr[2]);
+    std::vector<std::vector<int32_t>> I(hdr[2]);
+    std::vector<b200pt_mesh> meshes(hdr[2]);
+    for (uint32_t m = 0; m < hdr[2]; ++m) {
+        int32_t obj; uint32_t nv, nt;
+        if (fread(&obj, 4, 1, f) != 1 || fread(&nv, 4, 1, f) != 1 || fread(&nt, 4, 1, f) != 1) return 2;
+        P[m].resize(3 * size_t(nv)); I[m].resize(3 * size_t(nt));
+        if (fread(P[m].data(), 4, P[m].size(), f) != P[m].size()) return 2;
+        if (fread(I[m].data(), 4, I[m].size(), f) != I[m].size()) return 2;
+        meshes[m] = b200pt_mesh{obj, nv, nt, P[m].data(), I[m].data()};
+    }
+    fclose(f);
+    b200pt_scene_desc desc{};
+    desc.n_meshes = hdr[2];
+    desc.meshes = meshes.data();
+    HostScene hs;
+    std::string err;
+    if (AssembleScene(&desc, hs, err) != 0) { fprintf(stderr, "%s\n", err.c_str()); return 3; }
+    FILE *rf = fopen(argv[2], "rb");
+    fseek(rf, 0, SEEK_END);
+    size_t n = ftell(rf) / 28;
+    fseek(rf, 0, SEEK_SET);
+    std::vector<float> rays(n * 7);
+    if (fread(rays.data(), 4, rays.size(), rf) != rays.size()) return 2;
+    fclose(rf);
+    bool any = std::string(argv[3]) == "any";
+    std::vector<b200pt_hit> hits(any ? 0 : n);
+    std::vector<uint8_t> occ(any ? n : 0);
+    for (size_t i = 0; i < n; ++i) {
+        const float *q = &rays[7 * i];
+        RayCtx r;
+        RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
+        float tMax = q[6];
+        int stack[64], sp = 0, cur = int(hs.rootNode), best = -1;
+        float bb1 = 0, bb2 = 0;
+        bool hitAny = false;
+        while (true) {
+            const Node32 &nd = hs.nodes[cur];
+            if (SlabTest(r, nd.bmin, nd.bmax, tMax)) {
+                if (nd.nPrims > 0) {
+                    for (int k = 0; k < nd.nPrims && !hitAny; ++k) {
+                        const PrimSlot &s = hs.prims[nd.offset + k];
+                        float t, b0, b1, b2;
+                        if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
+                            if (any) { hitAny = true; break; }
+                            tMax = t; best = nd.offset + k; bb1 = b1; bb2 = b2;
+                        }
+                    }
+                    if (hitAny || sp == 0) break;
+                    cur = stack[--sp];
+                } else if (r.neg[nd.axis]) {
+                    stack[sp++] = cur + 1;
+                    cur = nd.offset;
+                } else {
+                    stack[sp++] = nd.offset;
+                    cur = cur + 1;
+                }
+            } else {
+                if (sp == 0) break;
+                cur = stack[--sp];
+            }
+        }
+        if (any) occ[i] = hitAny;
+        else if (best < 0) hits[i] = b200pt_hit{0xFFFFFFFFu, 0, 0, 0, 0, 0};
+        else hits[i] = b200pt_hit{hs.prims[best].mesh, hs.prims[best].tri, 0, tMax, bb1, bb2};
+    }
+    FILE *of = fopen(argv[4], "wb");
+    if (any) fwrite(occ.data(), 1, n, of); else fwrite(hits.data(), sizeof(b200pt_hit), n, of);
+    fclose(of);
+    return 0;
+}
