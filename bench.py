@@ -180,7 +180,8 @@ def main():
 
     # ---- scene (replicated) and this rank's batches
     sc = P.scenes.random_soup(args.tris, seed=12111)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()  # the library launches on this stream; torch events are recorded on it
+    torch.cuda.set_stream(stream)
     agg = P.B200Aggregate(sc, device=local, stream=stream.cuda_stream)
     st = agg.stats()
     n = args.rays

@@ -138,7 +138,8 @@ enum { B200PT_TRACE_COUNTERS = 1u << 8 };
 int b200pt_version(void);
 int b200pt_device_count(int *count);
 int b200pt_context_create(int device, b200pt_ctx **out);
-/* run on an existing CUDA stream (cudaStream_t passed as void*); NULL = own stream */
+/* run on the caller's CUDA stream (cudaStream_t passed as void*; NULL = the legacy default
+ * stream) instead of the context's own non-blocking stream */
 int b200pt_context_set_stream(b200pt_ctx *ctx, void *cuda_stream);
 int b200pt_context_sync(b200pt_ctx *ctx);
 int b200pt_context_destroy(b200pt_ctx *ctx);

@@ -117,12 +117,7 @@ int b200pt_context_set_stream(b200pt_ctx *ctx, void *cuda_stream) {
         cudaStreamDestroy(ctx->stream);
         ctx->ownStream = false;
     }
-    if (cuda_stream) {
-        ctx->stream = (cudaStream_t)cuda_stream;
-    } else {
-        B2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-        ctx->ownStream = true;
-    }
+    ctx->stream = (cudaStream_t)cuda_stream;  // NULL = the legacy default stream
     return B200PT_OK;
 }
 
