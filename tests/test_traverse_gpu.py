@@ -99,8 +99,8 @@ def test_invalid_scene_is_an_error_not_a_crash(P):
 
 def test_full_size_properties_1m_triangles(P):
     """BASELINE config 2 at full size (1M triangles, 2^22 rays here): properties that need no oracle.
-    (a) any-hit(o,d,tMax) == closest-hit exists; (b) re-tracing with tMax = t_hit returns the same
-    triangle with the same t (triangles accept t == tMax, shapes.cpp:239-242); (c) with tMax just
+    (a) any-hit(o,d,tMax) == closest-hit exists; (b) re-tracing with tMax just beyond t_hit returns the
+    same record; (c) with tMax just
     below t_hit the first hit is never returned; (d) counters are consistent."""
     sc = P.scenes.random_soup(1_000_000, seed=12111)
     agg = P.B200Aggregate(sc)
@@ -113,15 +113,12 @@ def test_full_size_properties_1m_triangles(P):
     hit = hits["mesh"] != 0xFFFFFFFF
     assert hit.mean() > 0.99
     assert np.array_equal(agg.IntersectShadow(rays) != 0, hit)
+    # re-tracing with tMax a hair beyond t_hit finds the same hit (t itself is not guaranteed to be
+    # accepted again: the range test is on tScaled vs tMax*det, shapes.cpp:239-242, and t*det rounds)
     again = rays.copy()
-    again[:, 6] = np.where(hit, hits["t"], np.inf)
+    again[:, 6] = np.where(hit, hits["t"] * np.float32(1.00001), np.inf)
     h2 = agg.IntersectClosest(again)
-    # identical except where another triangle's rounded tScaled test lets it in at t ~ tMax (order-dependent
-    # in the reference too): ids may then differ, t may not move by more than an ulp or two
-    same = (h2["mesh"] == hits["mesh"]) & (h2["prim"] == hits["prim"]) & (h2["t"].view("u4") == hits["t"].view("u4"))
-    assert same.mean() > 0.9999, f"{(~same).sum()} of {same.size} re-traced rays changed"
-    assert (h2["mesh"][hit] != 0xFFFFFFFF).all()
-    assert (np.abs(h2["t"][hit].view("i4").astype(np.int64) - hits["t"][hit].view("i4")) <= 2).all()
+    assert np.array_equal(h2.view("u1"), hits.view("u1"))
     below = rays.copy()
     below[:, 6] = np.nextafter(hits["t"], np.float32(0))
     h3 = agg.IntersectClosest(below[hit])
