@@ -22,6 +22,7 @@ CPP_SOURCES = ["bvh2_build.cpp", "scene_host.cpp", "api.cpp"]
 # (file, extra nvcc flags)
 CU_SOURCES = [
     ("traverse_bvh2.cu", ["--fmad=false"]),
+    ("traverse_persist.cu", ["--fmad=false"]),
 ]
 
 

@@ -3,8 +3,10 @@
 // exists anywhere below: if there is no device, context creation fails.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -30,14 +32,17 @@ struct b200pt_ctx {
     size_t dInCap = 0;
     void *dOut = nullptr;
     size_t dOutCap = 0;
-    unsigned long long *dCounters = nullptr;
+    unsigned long long *dCounters = nullptr;  // [0..2] trace counters, [7] ray-fetch counter
+    // scheduling knobs of the persistent kernel (B200PT_REFILL_MIN / B200PT_NODE_MIN override)
+    int refillMin = 4, nodeMin = 16;
+    bool simpleKernel = false;  // B200PT_TRAVERSAL=simple: the one-thread-per-ray parity kernel
 };
 
 struct b200pt_scene {
     b200pt_ctx *ctx = nullptr;
     HostScene host;
     DeviceScene dev{};
-    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr;
+    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr, *dPairs = nullptr;
     b200pt_scene_stats stats{};
     b200pt_trace_stats trace{};
 };
@@ -105,6 +110,10 @@ int b200pt_context_create(int device, b200pt_ctx **out) {
         return B200PT_ERR_CUDA;
     }
     c->ownStream = true;
+    const char *mode = getenv("B200PT_TRAVERSAL");
+    c->simpleKernel = mode && std::string(mode) == "simple";
+    if (const char *v = getenv("B200PT_REFILL_MIN")) c->refillMin = std::max(1, std::min(32, atoi(v)));
+    if (const char *v = getenv("B200PT_NODE_MIN")) c->nodeMin = std::max(1, std::min(32, atoi(v)));
     *out = c;
     return B200PT_OK;
 }
@@ -160,6 +169,10 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     cudaError_t e = cudaSetDevice(ctx->device);
     if (e == cudaSuccess) e = cudaMalloc(&s->dNodes, nodeBytes);
     if (e == cudaSuccess) e = cudaMalloc(&s->dPrims, primBytes);
+    size_t pairBytes = std::max<size_t>(h.pairs.size(), 1) * sizeof(PairNode);
+    if (e == cudaSuccess) e = cudaMalloc(&s->dPairs, pairBytes);
+    if (e == cudaSuccess && !h.pairs.empty())
+        e = cudaMemcpyAsync(s->dPairs, h.pairs.data(), h.pairs.size() * sizeof(PairNode), cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(s->dNodes, h.nodes.data(), nodeBytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(s->dPrims, h.prims.data(), primBytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -170,16 +183,20 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     }
     s->dev.nodes = s->dNodes;
     s->dev.prims = s->dPrims;
+    s->dev.pairs = s->dPairs;
+    std::memcpy(s->dev.rootBox, h.bounds, 24);
+    s->dev.rootRef = h.rootRef;
     s->dev.instances = nullptr;
     s->dev.rootNode = h.rootNode;
     s->dev.nNodes = uint32_t(h.nodes.size());
     s->dev.nPrims = uint32_t(h.prims.size());
     s->dev.nInstances = 0;
+    s->dev.maxDepth = h.maxDepth;
     s->stats.n_triangles = h.nTriangles;
     s->stats.n_instances = 0;
     s->stats.n_bvh2_nodes = h.nodes.size();
-    s->stats.n_wide_nodes = 0;
-    s->stats.device_bytes = nodeBytes + primBytes;
+    s->stats.n_wide_nodes = h.pairs.size();
+    s->stats.device_bytes = nodeBytes + primBytes + pairBytes;
     s->stats.build_seconds = h.buildSeconds;
     s->stats.upload_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     *out = s;
@@ -192,6 +209,7 @@ int b200pt_scene_destroy(b200pt_scene *s) {
     cudaStreamSynchronize(s->ctx->stream);
     if (s->dNodes) cudaFree(s->dNodes);
     if (s->dPrims) cudaFree(s->dPrims);
+    if (s->dPairs) cudaFree(s->dPairs);
     if (s->dInst) cudaFree(s->dInst);
     delete s;
     return B200PT_OK;
@@ -252,9 +270,16 @@ static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, u
     }
     if (count) B2_CUDA(ctx, cudaMemsetAsync(ctx->dCounters, 0, 8 * sizeof(unsigned long long), ctx->stream));
     B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    B2_CUDA(ctx, LaunchTraverseBVH2(s->dev, dRays, n, any ? nullptr : (b200pt_hit *)dOut,
-                                    any ? (unsigned char *)dOut : nullptr, any,
-                                    count ? ctx->dCounters : nullptr, ctx->smCount, ctx->stream));
+    if (ctx->simpleKernel)
+        B2_CUDA(ctx, LaunchTraverseBVH2(s->dev, dRays, n, any ? nullptr : (b200pt_hit *)dOut,
+                                        any ? (unsigned char *)dOut : nullptr, any,
+                                        count ? ctx->dCounters : nullptr, ctx->smCount, ctx->stream));
+    else
+        B2_CUDA(ctx, LaunchTraversePersist(s->dev, dRays, n, any ? nullptr : (b200pt_hit *)dOut,
+                                           any ? (unsigned char *)dOut : nullptr, any,
+                                           (int *)(ctx->dCounters + 7), count ? ctx->dCounters : nullptr,
+                                           ctx->smCount, int(s->dev.maxDepth) + 1, ctx->refillMin, ctx->nodeMin,
+                                           ctx->stream));
     B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     if (!device) {
         B2_CUDA(ctx, cudaMemcpyAsync(out, dOut, size_t(n) * outRec, cudaMemcpyDeviceToHost, ctx->stream));

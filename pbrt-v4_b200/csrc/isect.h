@@ -95,26 +95,37 @@ B2_HD void RaySetup(RayCtx &r, float ox, float oy, float oz, float dx, float dy,
     r.Sz = B2_DIV(1.f, pdz);
 }
 
-// Bounds3::IntersectP with precomputed invDir/dirIsNeg.
-B2_HD bool SlabTest(const RayCtx &r, const float *bmin, const float *bmax, float raytMax) {
+// Bounds3::IntersectP with precomputed invDir/dirIsNeg.  Branch-free: the reference's two early
+// `return false` only skip work, so evaluating everything and AND-ing the conditions gives the same
+// boolean (selects keep the reference's NaN behaviour: `a > b ? a : b`, not fmax).
+// SlabCore returns every part of the test that does not involve the ray's tMax, and the entry
+// distance tMin; the full test is `SlabCore(...) && tMin < raytMax`.  The split matters: a child
+// pushed on the stack must have its `tMin < raytMax` part evaluated when it is POPPED, with the
+// tMax of that moment, because the reference's tMax is not monotone - an accepted triangle's
+// t = tScaled * invDet can round to just above the tMax it was tested against (shapes.cpp:239-250).
+B2_HD bool SlabCore(const RayCtx &r, const float *bmin, const float *bmax, float &tMinOut) {
     float tMin = B2_MUL(B2_SUB((r.neg[0] ? bmax[0] : bmin[0]), r.ox), r.ix);
     float tMax = B2_MUL(B2_SUB((r.neg[0] ? bmin[0] : bmax[0]), r.ox), r.ix);
     float tyMin = B2_MUL(B2_SUB((r.neg[1] ? bmax[1] : bmin[1]), r.oy), r.iy);
     float tyMax = B2_MUL(B2_SUB((r.neg[1] ? bmin[1] : bmax[1]), r.oy), r.iy);
-    tMax = B2_MUL(tMax, kSlabPad);
-    tyMax = B2_MUL(tyMax, kSlabPad);
-    if (tMin > tyMax || tyMin > tMax)
-        return false;
-    if (tyMin > tMin) tMin = tyMin;
-    if (tyMax < tMax) tMax = tyMax;
     float tzMin = B2_MUL(B2_SUB((r.neg[2] ? bmax[2] : bmin[2]), r.oz), r.iz);
     float tzMax = B2_MUL(B2_SUB((r.neg[2] ? bmin[2] : bmax[2]), r.oz), r.iz);
+    tMax = B2_MUL(tMax, kSlabPad);
+    tyMax = B2_MUL(tyMax, kSlabPad);
     tzMax = B2_MUL(tzMax, kSlabPad);
-    if (tMin > tzMax || tzMin > tMax)
-        return false;
-    if (tzMin > tMin) tMin = tzMin;
-    if (tzMax < tMax) tMax = tzMax;
-    return (tMin < raytMax) && (tMax > 0);
+    bool ok = !(tMin > tyMax) & !(tyMin > tMax);
+    tMin = tyMin > tMin ? tyMin : tMin;
+    tMax = tyMax < tMax ? tyMax : tMax;
+    ok &= !(tMin > tzMax) & !(tzMin > tMax);
+    tMin = tzMin > tMin ? tzMin : tMin;
+    tMax = tzMax < tMax ? tzMax : tMax;
+    tMinOut = tMin;
+    return ok & (tMax > 0);
+}
+
+B2_HD bool SlabTest(const RayCtx &r, const float *bmin, const float *bmax, float raytMax) {
+    float tMin;
+    return SlabCore(r, bmin, bmax, tMin) & (tMin < raytMax);
 }
 
 B2_HD float Max3Abs(float a, float b, float c) {

@@ -11,4 +11,9 @@ cudaError_t LaunchTraverseBVH2(const DeviceScene &sc, const float *rays, long lo
                                unsigned char *occluded, bool any, unsigned long long *counters,
                                int smCount, cudaStream_t stream);
 
+cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long long n, b200pt_hit *hits,
+                                  unsigned char *occluded, bool any, int *rayCounter,
+                                  unsigned long long *counters, int smCount, int stackDepth,
+                                  int refillMin, int nodeMin, cudaStream_t stream);
+
 }  // namespace b200pt

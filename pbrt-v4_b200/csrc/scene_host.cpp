@@ -194,6 +194,53 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             out.nodes.push_back(nd);
         }
     }
+    // ---- production layout: interior nodes only, children's boxes in the parent
+    out.pairs.clear();
+    out.treeRootRef.clear();
+    {
+        std::vector<int32_t> refOf(out.nodes.size());
+        int32_t nPairs = 0;
+        for (size_t i = 0; i < out.nodes.size(); ++i) {
+            const Node32 &nd = out.nodes[i];
+            refOf[i] = nd.nPrims == 0 ? nPairs++ : ~nd.offset;
+            if (nd.nPrims > 0)
+                out.prims[nd.offset].flags = nd.nPrims;  // leaf header: count in its first slot
+        }
+        out.pairs.resize(nPairs);
+        for (size_t i = 0; i < out.nodes.size(); ++i) {
+            const Node32 &nd = out.nodes[i];
+            if (nd.nPrims != 0)
+                continue;
+            PairNode &pn = out.pairs[refOf[i]];
+            const Node32 &c0 = out.nodes[i + 1], &c1 = out.nodes[nd.offset];
+            std::memcpy(pn.box0, c0.bmin, 12);
+            std::memcpy(pn.box0 + 3, c0.bmax, 12);
+            std::memcpy(pn.box1, c1.bmin, 12);
+            std::memcpy(pn.box1 + 3, c1.bmax, 12);
+            pn.ref0 = refOf[i + 1];
+            pn.ref1 = refOf[nd.offset];
+            pn.axis = nd.axis;
+            pn.pad = 0;
+        }
+        for (uint32_t r : out.treeRoot)
+            out.treeRootRef.push_back(refOf[r]);
+        out.rootRef = out.treeRootRef[0];
+    }
+    // deepest root-to-leaf path (sizes the traversal stack; the reference's is a fixed 64)
+    out.maxDepth = 1;
+    for (size_t ti = 0; ti < out.trees.size(); ++ti) {
+        std::vector<std::pair<uint32_t, uint32_t>> st{{out.treeRoot[ti], 1u}};
+        while (!st.empty()) {
+            auto [i, d] = st.back();
+            st.pop_back();
+            out.maxDepth = std::max(out.maxDepth, d);
+            const Node32 &nd = out.nodes[i];
+            if (nd.nPrims == 0) {
+                st.push_back({i + 1, d + 1});
+                st.push_back({uint32_t(nd.offset), d + 1});
+            }
+        }
+    }
     out.rootNode = out.treeRoot[0];
     const Node32 &root = out.nodes[out.rootNode];
     std::memcpy(out.bounds, root.bmin, 12);

@@ -23,9 +23,13 @@ struct HostScene {
     std::vector<HostTree> trees;     // [0] = top level
     std::vector<Node32> nodes;       // all trees, absolute child / slot offsets
     std::vector<PrimSlot> prims;
+    std::vector<PairNode> pairs;     // production layout (interior nodes only)
+    std::vector<int32_t> treeRootRef; // per tree: PairNode index or ~slot
+    int32_t rootRef = 0;
     std::vector<InstanceDev> instances;
     std::vector<uint32_t> treeRoot;  // root node of trees[i] in `nodes`
     uint32_t rootNode = 0;
+    uint32_t maxDepth = 1;           // deepest path over all trees, in nodes
     float bounds[6] = {0, 0, 0, 0, 0, 0};
     uint64_t nTriangles = 0;
     double buildSeconds = 0;

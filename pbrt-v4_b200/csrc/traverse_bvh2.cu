@@ -60,8 +60,8 @@ TraverseBVH2Kernel(DeviceScene sc, const float *__restrict__ rays, long long n,
                     if (COUNT) ++cLeaves;
                     for (int k = 0; k < nd.nPrims; ++k) {
                         int slot = nd.offset + k;
-                        float4 a = __ldg(prims + 3 * slot), b = __ldg(prims + 3 * slot + 1),
-                               c = __ldg(prims + 3 * slot + 2);
+                        float4 a = __ldg(prims + 4 * slot), b = __ldg(prims + 4 * slot + 1),
+                               c = __ldg(prims + 4 * slot + 2);
                         float p0[3] = {a.x, a.y, a.z}, p1[3] = {a.w, b.x, b.y}, p2[3] = {b.z, b.w, c.x};
                         float t, b0, b1, b2;
                         if (COUNT) ++cPrims;
@@ -100,7 +100,7 @@ TraverseBVH2Kernel(DeviceScene sc, const float *__restrict__ rays, long long n,
             if (bestSlot < 0) {
                 h.mesh = kMissTag; h.prim = 0; h.instance = 0; h.t = 0; h.b1 = 0; h.b2 = 0;
             } else {
-                float4 c = __ldg(prims + 3 * bestSlot + 2);
+                float4 c = __ldg(prims + 4 * bestSlot + 2);
                 h.mesh = __float_as_uint(c.y);
                 h.prim = __float_as_uint(c.z);
                 h.instance = 0;

@@ -1,0 +1,252 @@
+// traverse_persist.cu - the production closest-hit / any-hit kernels over the binary tree.
+//
+// Same visit order as BVHAggregate::Intersect / IntersectP (reference
+// cpu/aggregates.cpp:529-624) - near child first by dirIsNeg[axis], far child
+// stacked - so ids / t stay bit-exact, but organised for the GPU:
+//   * persistent warps that pull rays from a global counter and REFILL idle
+//     lanes while the others keep traversing (the simple kernel ran at 5.8
+//     active threads per warp on incoherent rays: a warp waited for its longest ray);
+//   * "while-while": lanes iterate interior nodes until few are left, then the
+//     lanes parked at a leaf do their triangle tests together;
+//   * one 256-bit ld.global.nc per node (one L1 wavefront per lane instead of two)
+//     and a [depth][thread] shared-memory stack (conflict-free: 1 wavefront per
+//     warp push/pop; a local-memory stack is up to 32).
+// Arithmetic comes from isect.h unchanged.
+#include <cuda_runtime.h>
+
+#include "bvh2.h"
+#include "device_scene.h"
+#include "isect.h"
+#include "kernels.h"
+#include "../../include/b200pt.h"
+
+namespace b200pt {
+
+namespace {
+
+constexpr int kBlock = 128;
+
+struct Node8f {
+    float v[8];
+};
+
+__device__ __forceinline__ Node8f Load256(const void *p) {
+    Node8f n;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(n.v[0]), "=f"(n.v[1]), "=f"(n.v[2]), "=f"(n.v[3]), "=f"(n.v[4]), "=f"(n.v[5]),
+                   "=f"(n.v[6]), "=f"(n.v[7])
+                 : "l"(p));
+    return n;
+}
+
+enum : int { S_IDLE = 0, S_NODE = 1, S_LEAF = 2, S_DONE = 3 };
+
+}  // namespace
+
+// Traversal stack: the first kSmemDepth entries in shared memory laid out [depth][thread]
+// (conflict-free), the rare deeper ones in local memory.  An entry is {child ref, entry distance
+// tMin of its box}: the far child's box is tested when its parent is visited, and the only part of
+// the reference's test that depends on the ray's current tMax (`tMin < raytMax`,
+// util/vecmath.h:1609) is re-evaluated when the entry is popped - i.e. at the moment the
+// reference would have tested that node.
+constexpr int kSmemDepth = 24;
+constexpr int kLocalDepth = 72;
+
+template <bool ANY, bool COUNT>
+__global__ void __launch_bounds__(kBlock)
+TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200pt_hit *__restrict__ hits,
+                      unsigned char *__restrict__ occluded, int *__restrict__ rayCounter,
+                      unsigned long long *__restrict__ counters, int kRefillMin, int kNodeMin) {
+    __shared__ int2 smemStack[kSmemDepth * kBlock];
+    int2 *stack = smemStack + threadIdx.x;  // entry d lives at stack[d * kBlock]
+    int2 deep[kLocalDepth];
+    const char *pairs = reinterpret_cast<const char *>(sc.pairs);
+    const char *prims = reinterpret_cast<const char *>(sc.prims);
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+
+    int state = S_IDLE, rayIdx = -1;
+    bool exhausted = false;
+    RayCtx r;
+    float tMax = 0, bestB1 = 0, bestB2 = 0;
+    int cur = 0, sp = 0, bestSlot = -1;
+    unsigned long long cNodes = 0, cLeaves = 0, cPrims = 0;
+
+    auto push = [&](int ref, float t) {
+        int2 e = make_int2(ref, __float_as_int(t));
+        if (sp < kSmemDepth) stack[sp * kBlock] = e;
+        else deep[sp - kSmemDepth] = e;
+        ++sp;
+    };
+    // next entry whose box the reference would still enter with the current tMax; S_DONE if none
+    auto popNext = [&]() {
+        state = S_DONE;
+        while (sp > 0) {
+            --sp;
+            int2 e = sp < kSmemDepth ? stack[sp * kBlock] : deep[sp - kSmemDepth];
+            if (__int_as_float(e.y) < tMax) {
+                cur = e.x;
+                state = e.x < 0 ? S_LEAF : S_NODE;
+                break;
+            }
+        }
+    };
+
+    while (true) {
+        // ---- refill idle lanes from the global ray counter (one atomic per warp)
+        unsigned idle = __ballot_sync(FULL, state == S_IDLE);
+        if (idle) {
+            int nIdle = __popc(idle);
+            if (!exhausted && (nIdle >= kRefillMin || idle == FULL)) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(rayCounter, nIdle);
+                base = __shfl_sync(FULL, base, 0);
+                if (base + nIdle >= n) exhausted = true;
+                if (state == S_IDLE) {
+                    int my = base + __popc(idle & ((1u << lane) - 1));
+                    if (my < n) {
+                        const float *q = rays + 7ll * my;
+                        RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
+                        tMax = q[6];
+                        rayIdx = my;
+                        sp = 0;
+                        bestSlot = -1;
+                        // the reference tests the root's own box first (cpu/aggregates.cpp:545)
+                        if (COUNT) ++cNodes;
+                        if (SlabTest(r, sc.rootBox, sc.rootBox + 3, tMax)) {
+                            cur = sc.rootRef;
+                            state = cur < 0 ? S_LEAF : S_NODE;
+                        } else {
+                            state = S_DONE;
+                        }
+                    }
+                }
+                idle = __ballot_sync(FULL, state == S_IDLE);
+            }
+            if (idle == FULL && exhausted) break;
+        }
+
+        // ---- interior nodes: a warp-uniform loop (every lane evaluates the ballot, lanes that are not
+        // at an interior node skip the body), left when too few lanes still have interior work
+        unsigned inNode;
+        do {
+            if (state == S_NODE) {
+                if (COUNT) cNodes += 2;
+                Node8f a = Load256(pairs + 64ll * cur), b = Load256(pairs + 64ll * cur + 32);
+                float t0, t1;
+                bool h0 = SlabCore(r, a.v, a.v + 3, t0);
+                bool h1 = SlabCore(r, b.v, b.v + 3, t1);
+                int ref0 = __float_as_int(a.v[6]), ref1 = __float_as_int(b.v[6]);
+                int axis = __float_as_int(a.v[7]);
+                bool neg = (axis == 0 ? r.neg[0] : (axis == 1 ? r.neg[1] : r.neg[2])) != 0;
+                // near child first: dirIsNeg[axis] ? second : first (cpu/aggregates.cpp:562-568)
+                int nearRef = neg ? ref1 : ref0, farRef = neg ? ref0 : ref1;
+                float tNear = neg ? t1 : t0, tFar = neg ? t0 : t1;
+                // near child: visited now, so the whole test applies now.  far child: stacked on the
+                // tMax-independent part only; `tFar < tMax` is decided when it is popped (popNext).
+                bool hNear = (neg ? h1 : h0) & (tNear < tMax), hFar = neg ? h0 : h1;
+                if (hNear) {
+                    if (hFar) push(farRef, tFar);
+                    cur = nearRef;
+                    state = nearRef < 0 ? S_LEAF : S_NODE;
+                } else {
+                    if (hFar) push(farRef, tFar);
+                    popNext();
+                }
+            }
+            inNode = __ballot_sync(FULL, state == S_NODE);
+        } while (__popc(inNode) >= kNodeMin);
+
+        // ---- leaves: triangle tests, in slot order, later equal-t hit replaces earlier
+        if (state == S_LEAF) {
+            if (COUNT) ++cLeaves;
+            bool anyHit = false;
+            int slot = ~cur, leafN = 1;
+            for (int k = 0; k < leafN; ++k, ++slot) {
+                Node8f a = Load256(prims + 64ll * slot);
+                float4 b = __ldg(reinterpret_cast<const float4 *>(prims + 64ll * slot + 32));
+                if (k == 0) leafN = __float_as_int(b.w);  // leaf header: count in the first slot
+                float p0[3] = {a.v[0], a.v[1], a.v[2]}, p1[3] = {a.v[3], a.v[4], a.v[5]},
+                      p2[3] = {a.v[6], a.v[7], b.x};
+                float t, b0, b1, b2;
+                if (COUNT) ++cPrims;
+                if (TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2)) {
+                    if (ANY) {
+                        anyHit = true;
+                        break;
+                    }
+                    tMax = t;
+                    bestSlot = slot;
+                    bestB1 = b1;
+                    bestB2 = b2;
+                }
+            }
+            if (ANY && anyHit) {
+                bestSlot = 0;
+                state = S_DONE;
+            } else {
+                popNext();
+            }
+        }
+        __syncwarp();
+
+        // ---- finished rays write their record and go idle
+        if (state == S_DONE) {
+            if (ANY) {
+                occluded[rayIdx] = bestSlot >= 0 ? 1 : 0;
+            } else {
+                uint2 w0, w1, w2;
+                if (bestSlot < 0) {
+                    w0 = make_uint2(kMissTag, 0u);
+                    w1 = make_uint2(0u, 0u);
+                    w2 = make_uint2(0u, 0u);
+                } else {
+                    float4 b = __ldg(reinterpret_cast<const float4 *>(prims + 64ll * bestSlot + 32));
+                    w0 = make_uint2(__float_as_uint(b.y), __float_as_uint(b.z));
+                    w1 = make_uint2(0u, __float_as_uint(tMax));
+                    w2 = make_uint2(__float_as_uint(bestB1), __float_as_uint(bestB2));
+                }
+                uint2 *dst = reinterpret_cast<uint2 *>(hits + rayIdx);
+                dst[0] = w0;
+                dst[1] = w1;
+                dst[2] = w2;
+            }
+            state = S_IDLE;
+            bestSlot = -1;
+        }
+    }
+    if (COUNT) {
+        atomicAdd(counters + 0, cNodes);
+        atomicAdd(counters + 1, cLeaves);
+        atomicAdd(counters + 2, cPrims);
+    }
+}
+
+cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long long n, b200pt_hit *hits,
+                                  unsigned char *occluded, bool any, int *rayCounter,
+                                  unsigned long long *counters, int smCount, int stackDepth,
+                                  int refillMin, int nodeMin, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    if (n > 0x7fffffffll) return cudaErrorInvalidValue;
+    if (stackDepth > kSmemDepth + kLocalDepth) return cudaErrorInvalidValue;
+    size_t smemBytes = 0;
+    auto pick = [&](auto kern) -> cudaError_t {
+        int perSM = 0;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, kBlock, smemBytes);
+        if (e != cudaSuccess) return e;
+        if (perSM < 1) perSM = 1;
+        long long want = (n + kBlock - 1) / kBlock;
+        long long cap = (long long)smCount * perSM;  // persistent: exactly the resident set
+        int grid = (int)(want < cap ? want : cap);
+        e = cudaMemsetAsync(rayCounter, 0, sizeof(int), stream);
+        if (e != cudaSuccess) return e;
+        kern<<<grid, kBlock, smemBytes, stream>>>(sc, rays, (int)n, hits, occluded, rayCounter, counters, refillMin,
+                                                  nodeMin);
+        return cudaGetLastError();
+    };
+    if (any)
+        return counters ? pick(TraversePersistKernel<true, true>) : pick(TraversePersistKernel<true, false>);
+    return counters ? pick(TraversePersistKernel<false, true>) : pick(TraversePersistKernel<false, false>);
+}
+
+}  // namespace b200pt

@@ -3,7 +3,9 @@
 // traverse_bvh2.cu on the CPU, so the restated slab / triangle arithmetic can be
 // compared bit-for-bit with the compiled reference in the GPU-less container.
 // It is not part of libb200pt.so and nothing in the product calls it.
-//   hostcheck scene.b2sc rays.f32 {closest|any} out.bin
+//   hostcheck scene.b2sc rays.f32 {closest|any|closest2|any2} out.bin
+// closest2/any2 walk the production PairNode layout with the {ref, tMin} stack and the pop-time
+// `tMin < tMax` re-check exactly as traverse_persist.cu does.
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -45,10 +47,63 @@ int main(int argc, char **argv) {
     std::vector<float> rays(n * 7);
     if (fread(rays.data(), 4, rays.size(), rf) != rays.size()) return 2;
     fclose(rf);
-    bool any = std::string(argv[3]) == "any";
+    std::string mode = argv[3];
+    bool any = mode == "any" || mode == "any2";
+    bool pairMode = mode == "closest2" || mode == "any2";
     std::vector<b200pt_hit> hits(any ? 0 : n);
     std::vector<uint8_t> occ(any ? n : 0);
-    for (size_t i = 0; i < n; ++i) {
+    for (size_t i = 0; pairMode && i < n; ++i) {
+        const float *q = &rays[7 * i];
+        RayCtx r;
+        RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
+        float tMax = q[6];
+        struct E { int ref; float t; };
+        E stack[128];
+        int sp = 0, cur = 0, best = -1;
+        float bb1 = 0, bb2 = 0;
+        bool hitAny = false, done = false;
+        auto popNext = [&]() {
+            done = true;
+            while (sp > 0) {
+                E e = stack[--sp];
+                if (e.t < tMax) { cur = e.ref; done = false; break; }
+            }
+        };
+        if (SlabTest(r, hs.bounds, hs.bounds + 3, tMax)) cur = hs.rootRef; else done = true;
+        while (!done) {
+            if (cur >= 0) {
+                const PairNode &pn = hs.pairs[cur];
+                float t0, t1;
+                bool h0 = SlabCore(r, pn.box0, pn.box0 + 3, t0);
+                bool h1 = SlabCore(r, pn.box1, pn.box1 + 3, t1);
+                if (getenv("RAYDBG") && (size_t)atol(getenv("RAYDBG")) == i)
+                    fprintf(stderr, "pair %d: h0 %d t0 %g ref0 %d | h1 %d t1 %g ref1 %d | tMax %.9g\n", cur, h0, t0, pn.ref0, h1, t1, pn.ref1, tMax);
+                bool neg = r.neg[pn.axis] != 0;
+                int nearRef = neg ? pn.ref1 : pn.ref0, farRef = neg ? pn.ref0 : pn.ref1;
+                float tNear = neg ? t1 : t0, tFar = neg ? t0 : t1;
+                bool hNear = (neg ? h1 : h0) && (tNear < tMax), hFar = neg ? h0 : h1;
+                if (hFar) stack[sp++] = E{farRef, tFar};
+                if (hNear) cur = nearRef;
+                else popNext();
+            } else {
+                int slot = ~cur, cnt = int(hs.prims[slot].flags);
+                for (int k = 0; k < cnt; ++k, ++slot) {
+                    const PrimSlot &s = hs.prims[slot];
+                    float t, b0, b1, b2;
+                    if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
+                        if (any) { hitAny = true; break; }
+                        tMax = t; best = slot; bb1 = b1; bb2 = b2;
+                    }
+                }
+                if (hitAny) break;
+                popNext();
+            }
+        }
+        if (any) occ[i] = hitAny;
+        else if (best < 0) hits[i] = b200pt_hit{0xFFFFFFFFu, 0, 0, 0, 0, 0};
+        else hits[i] = b200pt_hit{hs.prims[best].mesh, hs.prims[best].tri, 0, tMax, bb1, bb2};
+    }
+    for (size_t i = 0; !pairMode && i < n; ++i) {
         const float *q = &rays[7 * i];
         RayCtx r;
         RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
@@ -58,6 +113,10 @@ int main(int argc, char **argv) {
         bool hitAny = false;
         while (true) {
             const Node32 &nd = hs.nodes[cur];
+            if (getenv("RAYDBG") && (size_t)atol(getenv("RAYDBG")) == i) {
+                float tm; bool h = SlabCore(r, nd.bmin, nd.bmax, tm) && tm < tMax;
+                fprintf(stderr, "node %d: h %d tmin %g nprims %d off %d tMax %.9g\n", cur, h, tm, nd.nPrims, nd.offset, tMax);
+            }
             if (SlabTest(r, nd.bmin, nd.bmax, tMax)) {
                 if (nd.nPrims > 0) {
                     for (int k = 0; k < nd.nPrims && !hitAny; ++k) {

@@ -11,11 +11,13 @@ import pytest
 from conftest import hit_mismatches
 
 
-def run_hostcheck(binpath, P, rs, rays):
+def run_hostcheck(binpath, P, rs, rays, layout="pair"):
+    """layout "pair" = the production PairNode walk (traverse_persist.cu), "node32" = the parity kernel's."""
+    sfx = "2" if layout == "pair" else ""
     rp = os.path.join(rs.dir, "rays_hc.f32")
     np.ascontiguousarray(rays, "<f4").tofile(rp)
-    subprocess.check_call([binpath, rs.path, rp, "closest", rs.dir + "/hc_hits.bin"])
-    subprocess.check_call([binpath, rs.path, rp, "any", rs.dir + "/hc_occ.bin"])
+    subprocess.check_call([binpath, rs.path, rp, "closest" + sfx, rs.dir + "/hc_hits.bin"])
+    subprocess.check_call([binpath, rs.path, rp, "any" + sfx, rs.dir + "/hc_occ.bin"])
     return (np.fromfile(rs.dir + "/hc_hits.bin", dtype=P.capi.HIT_DTYPE),
             np.fromfile(rs.dir + "/hc_occ.bin", dtype=np.uint8))
 
@@ -30,8 +32,9 @@ CASES = {
 }
 
 
+@pytest.mark.parametrize("layout", ["pair", "node32"])
 @pytest.mark.parametrize("case", sorted(CASES))
-def test_host_arithmetic_bit_exact(P, refrun, hostcheck_bin, case):
+def test_host_arithmetic_bit_exact(P, refrun, hostcheck_bin, case, layout):
     S = P.scenes
     sc, kind = CASES[case](S)
     if kind == "primary":
@@ -43,7 +46,7 @@ def test_host_arithmetic_bit_exact(P, refrun, hostcheck_bin, case):
     rs = refrun.RefScene(sc)
     ref, _ = rs.closest(rays)
     occ_ref, _ = rs.any(rays)
-    mine, occ = run_hostcheck(hostcheck_bin, P, rs, rays)
+    mine, occ = run_hostcheck(hostcheck_bin, P, rs, rays, layout)
     assert (ref["mesh"] != 0xFFFFFFFF).mean() > 0.3
     assert hit_mismatches(mine, ref).sum() == 0
     assert (occ != occ_ref).sum() == 0
@@ -51,6 +54,6 @@ def test_host_arithmetic_bit_exact(P, refrun, hostcheck_bin, case):
     sh = S.shadow_rays(rays, mine)
     ref2, _ = rs.closest(sh)
     occ_ref2, _ = rs.any(sh)
-    mine2, occ2 = run_hostcheck(hostcheck_bin, P, rs, sh)
+    mine2, occ2 = run_hostcheck(hostcheck_bin, P, rs, sh, layout)
     assert hit_mismatches(mine2, ref2).sum() == 0
     assert (occ2 != occ_ref2).sum() == 0

