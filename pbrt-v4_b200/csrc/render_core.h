@@ -1,0 +1,187 @@
+// render_core.h - the per-path logic of the render kernels as host+device inline functions:
+// sampler, wavelengths, camera, surface interaction, BSDFs, light sampling, one path-vertex step.
+// The kernels in render.cu are thin loops over these; tests/native/rendercheck.cpp runs the very
+// same functions on the CPU so the pipeline can be debugged against pbrt_ref without a GPU.
+//
+// Sampler dimensions are consumed in the order of the reference's CPU PathIntegrator
+// (cpu/integrators.cpp:228-290 EvaluatePixelSample, :629-762 Li, :764-805 SampleLd), which is the
+// image oracle, so with the same sampler the paths track the reference's paths.
+#pragma once
+#include "device_scene.h"
+#include "render_math.h"
+#include "render_types.h"
+
+namespace b200pt {
+
+// ------------------------------------------------------------------ ZSobol sampler (samplers.h:224-370)
+struct ZSobol {
+    int log2Spp, nBase4Digits, seed;
+    uint32_t randomize;
+    uint64_t mortonIndex;
+    int dimension;
+};
+
+B2_HD uint64_t LeftShift2(uint64_t x) {  // util/math.h:83-91
+    x &= 0xffffffff;
+    x = (x ^ (x << 16)) & 0x0000ffff0000ffffull;
+    x = (x ^ (x << 8)) & 0x00ff00ff00ff00ffull;
+    x = (x ^ (x << 4)) & 0x0f0f0f0f0f0f0f0full;
+    x = (x ^ (x << 2)) & 0x3333333333333333ull;
+    x = (x ^ (x << 1)) & 0x5555555555555555ull;
+    return x;
+}
+B2_HD uint64_t EncodeMorton2(uint32_t x, uint32_t y) { return (LeftShift2(y) << 1) | LeftShift2(x); }
+
+B2_HD void ZSobolStart(ZSobol &s, const SamplerDev &sd, int px, int py, int index, int dim) {
+    s.log2Spp = sd.log2Spp;
+    s.nBase4Digits = sd.nBase4Digits;
+    s.seed = sd.seed;
+    s.randomize = sd.randomize;
+    s.dimension = dim;
+    s.mortonIndex = (EncodeMorton2(px, py) << sd.log2Spp) | (uint64_t)index;
+}
+
+// the 24 permutations of 4 digits in the reference's order (samplers.h:300-326); packed 2 bits each
+B2_HD int ZSobolPermute(int p, int digit) {
+    const uint8_t perms[24] = {
+        // {a,b,c,d} -> a | b<<2 | c<<4 | d<<6
+        0 | 1 << 2 | 2 << 4 | 3 << 6, 0 | 1 << 2 | 3 << 4 | 2 << 6, 0 | 2 << 2 | 1 << 4 | 3 << 6,
+        0 | 2 << 2 | 3 << 4 | 1 << 6, 0 | 3 << 2 | 2 << 4 | 1 << 6, 0 | 3 << 2 | 1 << 4 | 2 << 6,
+        1 | 0 << 2 | 2 << 4 | 3 << 6, 1 | 0 << 2 | 3 << 4 | 2 << 6, 1 | 2 << 2 | 0 << 4 | 3 << 6,
+        1 | 2 << 2 | 3 << 4 | 0 << 6, 1 | 3 << 2 | 2 << 4 | 0 << 6, 1 | 3 << 2 | 0 << 4 | 2 << 6,
+        2 | 1 << 2 | 0 << 4 | 3 << 6, 2 | 1 << 2 | 3 << 4 | 0 << 6, 2 | 0 << 2 | 1 << 4 | 3 << 6,
+        2 | 0 << 2 | 3 << 4 | 1 << 6, 2 | 3 << 2 | 0 << 4 | 1 << 6, 2 | 3 << 2 | 1 << 4 | 0 << 6,
+        3 | 1 << 2 | 2 << 4 | 0 << 6, 3 | 1 << 2 | 0 << 4 | 2 << 6, 3 | 2 << 2 | 1 << 4 | 0 << 6,
+        3 | 2 << 2 | 0 << 4 | 1 << 6, 3 | 0 << 2 | 2 << 4 | 1 << 6, 3 | 0 << 2 | 1 << 4 | 2 << 6};
+    return (perms[p] >> (2 * digit)) & 3;
+}
+
+B2_HD uint64_t ZSobolSampleIndex(const ZSobol &s) {  // samplers.h:298-353
+    uint64_t sampleIndex = 0;
+    bool pow2Samples = s.log2Spp & 1;
+    int lastDigit = pow2Samples ? 1 : 0;
+    for (int i = s.nBase4Digits - 1; i >= lastDigit; --i) {
+        int digitShift = 2 * i - (pow2Samples ? 1 : 0);
+        int digit = (s.mortonIndex >> digitShift) & 3;
+        uint64_t higherDigits = s.mortonIndex >> (digitShift + 2);
+        int p = (MixBits(higherDigits ^ (0x55555555u * (uint32_t)s.dimension)) >> 24) % 24;
+        digit = ZSobolPermute(p, digit);
+        sampleIndex |= uint64_t(digit) << digitShift;
+    }
+    if (pow2Samples) {
+        int digit = s.mortonIndex & 1;
+        sampleIndex |= digit ^ (MixBits((s.mortonIndex >> 1) ^ (0x55555555u * (uint32_t)s.dimension)) & 1);
+    }
+    return sampleIndex;
+}
+
+// Sobol' generator matrices of dimensions 0 and 1 (the only ones ZSobol uses): dimension 0 is the
+// van der Corput radical inverse, dimension 1 has column j = binomial(j, i) mod 2 - the same values
+// as SobolMatrices32[0..103] (util/sobolmatrices.cpp:40-58; checked in tests/test_render_core.py).
+B2_HD uint32_t SobolColumn(int dim, int j) {
+    if (dim == 0) return j < 32 ? (0x80000000u >> j) : 0u;
+    uint32_t v = 0;
+    for (int i = 0; i < 32; ++i)
+        if ((i & ~j) == 0) v |= 0x80000000u >> i;
+    return v;
+}
+B2_HD uint32_t FastOwen(uint32_t v, uint32_t seed) {  // util/lowdiscrepancy.h:221-237
+    v = ReverseBits32(v);
+    v ^= v * 0x3d20adea;
+    v += seed;
+    v *= (seed >> 16) | 1;
+    v ^= v * 0x05526c56;
+    v ^= v * 0x53a22864;
+    return ReverseBits32(v);
+}
+B2_HD uint32_t OwenScramble(uint32_t v, uint32_t seed) {  // util/lowdiscrepancy.h:240-262
+    if (seed & 1) v ^= 1u << 31;
+    for (int b = 1; b < 32; ++b) {
+        uint32_t mask = (~0u) << (32 - b);
+        if ((uint32_t)MixBits((v & mask) ^ seed) & (1u << b)) v ^= 1u << (31 - b);
+    }
+    return v;
+}
+B2_HD float SobolSampleZ(uint64_t a, int dim, uint32_t randomize, uint32_t hash) {  // util/lowdiscrepancy.h:168-180
+    uint32_t v = 0;
+    if (dim == 0) {
+        v = ReverseBits32((uint32_t)a);  // sum of 0x80000000 >> j over set bits j < 32
+    } else {
+        for (int j = 0; a != 0; a >>= 1, ++j)
+            if (a & 1) v ^= SobolColumn(1, j);
+    }
+    if (randomize == 1) v ^= hash;
+    else if (randomize == 2) v = FastOwen(v, hash);
+    else if (randomize == 3) v = OwenScramble(v, hash);
+    return fminf(v * 0x1p-32f, kOneMinusEps);
+}
+B2_HD float ZSobolGet1D(ZSobol &s) {  // samplers.h:258-272
+    uint64_t idx = ZSobolSampleIndex(s);
+    ++s.dimension;
+    uint32_t h = (uint32_t)Hash2i(s.dimension, s.seed);
+    return SobolSampleZ(idx, 0, s.randomize, h);
+}
+B2_HD void ZSobolGet2D(ZSobol &s, float &u0, float &u1) {  // samplers.h:274-293
+    uint64_t idx = ZSobolSampleIndex(s);
+    s.dimension += 2;
+    uint64_t bits = Hash2i(s.dimension, s.seed);
+    u0 = SobolSampleZ(idx, 0, s.randomize, (uint32_t)bits);
+    u1 = SobolSampleZ(idx, 1, s.randomize, (uint32_t)(bits >> 32));
+}
+
+// ------------------------------------------------------------------ wavelengths and spectra
+// SampledWavelengths::SampleUniform (util/spectrum.h:318-336): all 31 wavelengths follow from u.
+B2_HD void SampleWavelengths(float u, float lambda[kNLambda]) {
+    lambda[0] = Lerp(u, kLambdaMin, kLambdaMax);
+    float delta = (kLambdaMax - kLambdaMin) / kNLambda;
+    for (int i = 1; i < kNLambda; ++i) {
+        lambda[i] = lambda[i - 1] + delta;
+        if (lambda[i] > kLambdaMax) lambda[i] = kLambdaMin + (lambda[i] - kLambdaMax);
+    }
+}
+B2_HD float SpectrumAt(const SpectrumTable &t, float lambda) {
+    if (t.interp == 0) {  // DenselySampledSpectrum::Sample (util/spectrum.h:420-430)
+        int offset = (int)lroundf(lambda) - (int)kLambdaMin;
+        return (offset < 0 || offset >= kSpecTable) ? 0.f : t.values[offset];
+    }
+    float x = lambda - kLambdaMin;
+    int i = (int)floorf(x);
+    if (i < 0) return t.values[0];
+    if (i >= kSpecTable - 1) return t.values[kSpecTable - 1];
+    return Lerp(x - i, t.values[i], t.values[i + 1]);
+}
+
+// ------------------------------------------------------------------ camera (cameras.cpp:433-456)
+B2_HD V3 XformPoint(const float *m, V3 p) {  // Transform::operator()(Point3) util/transform.h
+    float x = m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3];
+    float y = m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7];
+    float z = m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11];
+    float w = m[12] * p.x + m[13] * p.y + m[14] * p.z + m[15];
+    if (w == 1) return mk(x, y, z);
+    return mk(x, y, z) / w;
+}
+B2_HD V3 XformVector(const float *m, V3 v) {
+    return mk(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z,
+              m[8] * v.x + m[9] * v.y + m[10] * v.z);
+}
+B2_HD void GeneratePerspectiveRay(const CameraDev &c, float pFilmX, float pFilmY, float uLens0, float uLens1,
+                                  V3 &o, V3 &d) {
+    V3 pCamera = XformPoint(c.cameraFromRaster, mk(pFilmX, pFilmY, 0));
+    V3 ro = mk(0, 0, 0), rd = Normalize(pCamera);
+    if (c.lensRadius > 0) {
+        float lx, ly;
+        SampleUniformDiskConcentric(uLens0, uLens1, lx, ly);
+        lx *= c.lensRadius;
+        ly *= c.lensRadius;
+        float ft = c.focalDistance / rd.z;
+        V3 pFocus = ro + rd * ft;
+        ro = mk(lx, ly, 0);
+        rd = Normalize(pFocus - ro);
+    }
+    o = XformPoint(c.renderFromCamera, ro);
+    d = XformVector(c.renderFromCamera, rd);
+}
+
+}  // namespace b200pt
+
+#include "render_shade.h"

@@ -1,0 +1,123 @@
+// render_types.h - flat POD tables of the render path (camera .. film), device side.
+// Everything the shading kernels read is in these structs; no host pointers, no virtual
+// dispatch (the reference's TaggedPointer dispatch becomes a switch on a small tag).
+#pragma once
+#include <cstdint>
+
+namespace b200pt {
+
+constexpr int kNLambda = 31;          // NSpectrumSamples of the ISET fork (util/spectrum.h:36)
+constexpr float kLambdaMin = 395.f;   // Lambda_min / Lambda_max (util/spectrum.h:34-35)
+constexpr float kLambdaMax = 705.f;
+constexpr int kSpecTable = 311;       // 395..705 nm at 1 nm (DenselySampledSpectrum default range)
+
+struct Spec {
+    float v[kNLambda];
+};
+
+// One spectrum as a 1 nm table.  interp 0: nearest (DenselySampledSpectrum::Sample,
+// util/spectrum.h:420-430: lround(lambda) - lambda_min); interp 1: linear (stands in for the
+// smooth RGBAlbedoSpectrum / piecewise-linear spectra the host evaluated for us).
+struct SpectrumTable {
+    uint32_t interp;
+    float values[kSpecTable];
+};
+
+enum MaterialType : uint32_t { MAT_DIFFUSE = 0, MAT_CONDUCTOR = 1, MAT_DIELECTRIC = 2, MAT_COATED_DIFFUSE = 3, MAT_NONE = 0xFFFFFFFFu };
+
+struct MaterialDev {
+    uint32_t type;
+    int32_t spectrum[4];  // diffuse: [0] reflectance
+    float params[8];
+};
+
+// DiffuseAreaLight on one triangle (lights.h:410-470) + its alias-table bin (util/sampling.h:804).
+struct LightDev {
+    uint32_t type;       // 0 = diffuse area light on a triangle
+    uint32_t slot;       // PrimSlot of its triangle
+    int32_t spectrum;    // Lemit
+    float scale;
+    uint32_t twoSided;
+    float cosFalloffEnd, tanFalloffEnd, normalizeFalloffEnd;  // ISET spread angle (lights.cpp:716-718)
+    float aliasQ, aliasP;
+    int32_t alias;
+    uint32_t flipNormal; // mesh reverseOrientation ^ transformSwapsHandedness
+};
+
+struct MeshAttrDev {
+    int32_t material;
+    int32_t lightFirst;  // light index of triangle 0 of this mesh, -1 if not emissive
+    uint32_t flipNormal;
+    uint32_t pad;
+};
+
+struct CameraDev {
+    uint32_t type;               // 0 perspective (cameras.cpp:433-456)
+    float cameraFromRaster[16];  // row major
+    float renderFromCamera[16];
+    float lensRadius, focalDistance;
+};
+
+struct FilmDev {
+    uint32_t type;               // 0 = RGBFilm (film.h:232-310)
+    int32_t x0, y0, x1, y1;      // pixelBounds
+    int32_t fullResX, fullResY;
+    uint32_t filterType;         // 0 box
+    float filterRadiusX, filterRadiusY;
+    float imagingRatio;
+    float maxComponentValue;
+    float outputRGBFromSensorRGB[9];
+    int32_t sensorSpectrum[3];   // r_bar, g_bar, b_bar tables
+};
+
+struct SamplerDev {
+    uint32_t type;               // 0 = ZSobol (samplers.h:224-370), 1 = independent
+    int32_t samplesPerPixel;
+    int32_t seed;
+    uint32_t randomize;          // 0 none, 1 permutedigits, 2 fastowen, 3 owen
+    int32_t log2Spp;
+    int32_t nBase4Digits;
+};
+
+struct IntegratorDev {
+    int32_t maxDepth;
+    uint32_t regularize;
+    uint32_t lightSampler;       // 0 uniform, 1 power
+};
+
+struct RenderSceneDev {
+    CameraDev camera;
+    FilmDev film;
+    SamplerDev sampler;
+    IntegratorDev integrator;
+    const SpectrumTable *spectra;
+    const MaterialDev *materials;
+    const LightDev *lights;
+    const MeshAttrDev *meshes;
+    const void *prims;           // PrimSlot[] of the geometry scene
+    uint32_t nSpectra, nMaterials, nLights, nMeshes;
+};
+
+// Per-path state, structure of arrays over `n` paths of a pass.  Spectral arrays are [k][path].
+struct PathStateDev {
+    int n;
+    float *beta;       // 31 x n
+    float *L;          // 31 x n
+    float *Ld;         // 31 x n  pending direct-light contribution (already x beta), valid if shadowPending
+    float *rays;       // n x 7   next closest-hit ray
+    float *shadowRays; // n x 7
+    uint32_t *hits;    // n x 6   internal hit record {slot, t, b0, b1, b2, 0}
+    uint8_t *occluded; // n
+    int *pixel;        // pixel index in the film (y * width + x)
+    int *sampleIndex;
+    float *lambdaU;
+    int *dimension;    // sampler dimension consumed so far
+    int *depth;
+    uint32_t *flags;   // bit0 alive, bit1 specularBounce, bit2 anyNonSpecularBounces, bit3 shadowPending
+    float *etaScale;
+    float *pB;         // p_b of the last BSDF sample
+    float *prevCtx;    // n x 12: p, pError, n, ns of the previous vertex (LightSampleContext)
+    float *filterWeight;
+};
+
+}  // namespace b200pt
