@@ -161,6 +161,101 @@ int b200pt_intersect_any(b200pt_scene *scene, const float *rays, int64_t n,
                          uint8_t *occluded, uint32_t mem);
 int b200pt_get_trace_stats(const b200pt_scene *scene, b200pt_trace_stats *out);
 
+/* ------------------------------------------------------------------ render path
+ * b200pt_render_create replaces the object construction of RenderWavefront / the
+ * WavefrontPathIntegrator constructor (wavefront/wavefront.cpp:14-70, wavefront/integrator.cpp:89-199):
+ * the host (pbrt's parser + scene objects) hands over flat tables; b200pt_render_run replaces
+ * WavefrontPathIntegrator::Render (wavefront/integrator.cpp:290-493) for a range of sample indices;
+ * b200pt_film_* replace the film read-out before Film::WriteImage (film.cpp:542-574).
+ * Image parity is judged against the CPU PathIntegrator (cpu/integrators.cpp:629-805), whose
+ * sampler-dimension order the kernels follow. */
+
+/* spectrum = 311 values at 395..705 nm, 1 nm apart.  interp 0: nearest (DenselySampledSpectrum,
+ * util/spectrum.h:420-430); 1: linear between samples. */
+#define B200PT_SPECTRUM_SAMPLES 311
+typedef struct b200pt_spectrum {
+    uint32_t interp;
+    float values[B200PT_SPECTRUM_SAMPLES];
+} b200pt_spectrum;
+
+enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2, B200PT_MAT_COATED_DIFFUSE = 3 };
+typedef struct b200pt_material {
+    uint32_t type;
+    int32_t spectrum[4]; /* diffuse: [0] reflectance (materials.h:430-476) */
+    float params[8];
+} b200pt_material;
+
+/* DiffuseAreaLight on one triangle (lights.h:407-500) + its PowerLightSampler alias-table bin
+ * (lightsamplers.cpp:76-96, util/sampling.cpp:562-617).  Order = the host's `lights` vector. */
+typedef struct b200pt_light {
+    uint32_t mesh, tri;
+    int32_t spectrum; /* Lemit */
+    float scale;
+    uint32_t two_sided;
+    float cos_falloff_end, tan_falloff_end, normalize_falloff_end;
+    float alias_q, alias_p;
+    int32_t alias;
+} b200pt_light;
+
+typedef struct b200pt_mesh_attr {
+    int32_t material;    /* index into materials, -1 = interface (no BSDF) */
+    int32_t light_first; /* index of the light on triangle 0, -1 if not emissive */
+    uint32_t flip_normal; /* reverseOrientation ^ transformSwapsHandedness (util/mesh.h:42) */
+} b200pt_mesh_attr;
+
+typedef struct b200pt_render_desc {
+    /* camera: perspective (cameras.cpp:433-456) */
+    uint32_t camera_type;
+    float camera_from_raster[16];
+    float render_from_camera[16];
+    float lens_radius, focal_distance;
+    /* film: RGBFilm (film.h:232-310) with a box filter */
+    uint32_t film_type;
+    int32_t pixel_bounds[4]; /* x0 y0 x1 y1 */
+    int32_t full_resolution[2];
+    float filter_radius[2];
+    float imaging_ratio, max_component_value;
+    float output_rgb_from_sensor_rgb[9];
+    int32_t sensor_spectrum[3]; /* r_bar g_bar b_bar */
+    /* sampler: 0 = ZSobol (samplers.h:224-370) */
+    uint32_t sampler_type;
+    int32_t samples_per_pixel, seed;
+    uint32_t randomize; /* 0 none 1 permutedigits 2 fastowen 3 owen */
+    /* integrator: path (cpu/integrators.cpp:629-805) */
+    int32_t max_depth;
+    uint32_t regularize;
+    uint32_t light_sampler; /* 0 uniform, 1 power */
+    uint32_t n_spectra, n_materials, n_lights, n_meshes;
+    const b200pt_spectrum *spectra;
+    const b200pt_material *materials;
+    const b200pt_light *lights;
+    const b200pt_mesh_attr *meshes; /* one per mesh of the geometry scene */
+} b200pt_render_desc;
+
+typedef struct b200pt_render b200pt_render;
+
+typedef struct b200pt_render_stats {
+    uint64_t samples;        /* pixel samples completed by the last run */
+    uint64_t closest_rays, shadow_rays;
+    uint32_t kernel_launches;
+    float gpu_ms;            /* CUDA-event time of the last run */
+} b200pt_render_stats;
+
+int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b200pt_render **out);
+int b200pt_render_destroy(b200pt_render *r);
+/* Renders sample indices first, first+stride, ... (n_samples of them) of every pixel and adds them to
+ * the device film; asynchronous on the context's stream.  GPU g of G calls (g, spp/G, G): the union
+ * over GPUs is exactly the single-GPU sample set. */
+int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples, int32_t sample_stride);
+int b200pt_film_clear(b200pt_render *r);
+/* film accumulators {rgbSum[3], weightSum} as 4 doubles per pixel, row major over pixel_bounds
+ * (RGBFilm::Pixel, film.h:305-310).  device_ptr: for an in-place NCCL reduction by the host. */
+int b200pt_film_device_ptr(b200pt_render *r, void **ptr, uint64_t *n_doubles);
+int b200pt_film_read(b200pt_render *r, double *rgb_weight);
+/* final image, 3 floats per pixel: outputRGBFromSensorRGB * (rgbSum / weightSum) (film.h:261-277) */
+int b200pt_film_image(b200pt_render *r, float *rgb);
+int b200pt_render_get_stats(const b200pt_render *r, b200pt_render_stats *out);
+
 /* Host-only: build the binary SAH BVH for one primitive list exactly as the
  * reference does (cpu/aggregates.cpp:192-387, 505-522) and return it in the
  * LinearBVHNode layout.  bounds: n x 6 floats (pMin, pMax).  nodes_out must

@@ -1,0 +1,329 @@
+// oracle/dumpscene_ref.cpp - parses a .pbrt file with the REFERENCE's own parser and scene
+// construction (BasicSceneBuilder / BasicScene, the host side the north_star keeps) and writes the
+// flat tables a host adaptor would hand to b200pt_render_create as a `.b2rs`
+// container of named arrays.  TEST INFRASTRUCTURE ONLY (see oracle/raycast_ref.cpp header).
+//
+//   dumpscene_ref scene.pbrt out.b2rs
+//
+// Follows RenderCPU's construction order (cpu/render.cpp:25-55); reads private members of the
+// created objects (camera matrices, film sensor, alias table, BVH) in this one TU.
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+#define private public
+#define protected public
+#include <pbrt/pbrt.h>
+#include <pbrt/cameras.h>
+#include <pbrt/cpu/aggregates.h>
+#include <pbrt/cpu/primitive.h>
+#include <pbrt/film.h>
+#include <pbrt/filters.h>
+#include <pbrt/lights.h>
+#include <pbrt/lightsamplers.h>
+#include <pbrt/materials.h>
+#include <pbrt/options.h>
+#include <pbrt/parser.h>
+#include <pbrt/samplers.h>
+#include <pbrt/scene.h>
+#include <pbrt/shapes.h>
+#include <pbrt/textures.h>
+#include <pbrt/util/mesh.h>
+#include <pbrt/util/sampling.h>
+#include <pbrt/util/spectrum.h>
+#undef private
+#undef protected
+
+namespace pbrt {
+struct alignas(32) LinearBVHNode {  // layout of cpu/aggregates.cpp:129-137
+    Bounds3f bounds;
+    union {
+        int primitivesOffset;
+        int secondChildOffset;
+    };
+    uint16_t nPrimitives;
+    uint8_t axis;
+};
+}  // namespace pbrt
+using namespace pbrt;
+
+static void die(const std::string &msg) {
+    fprintf(stderr, "dumpscene_ref: %s\n", msg.c_str());
+    exit(2);
+}
+
+// ---- .b2rs container: 'B2RS', u32 count, then {u32 nameLen, name, u32 dtype (0 f32, 1 i32, 2 u32),
+// u32 ndim, u32 dims[], data}
+struct Writer {
+    FILE *f;
+    uint32_t count = 0;
+    explicit Writer(const char *fn) {
+        f = fopen(fn, "wb");
+        if (!f) die("cannot open output");
+        uint32_t hdr[2] = {0x53523242u, 0};
+        fwrite(hdr, 4, 2, f);
+    }
+    void put(const std::string &name, uint32_t dtype, std::vector<uint32_t> dims, const void *data) {
+        uint32_t nl = name.size(), nd = dims.size();
+        size_t n = 1;
+        for (uint32_t d : dims) n *= d;
+        fwrite(&nl, 4, 1, f);
+        fwrite(name.data(), 1, nl, f);
+        fwrite(&dtype, 4, 1, f);
+        fwrite(&nd, 4, 1, f);
+        fwrite(dims.data(), 4, nd, f);
+        if (n) fwrite(data, 4, n, f);
+        ++count;
+    }
+    void f32(const std::string &name, std::vector<uint32_t> dims, const std::vector<float> &v) { put(name, 0, dims, v.data()); }
+    void i32(const std::string &name, std::vector<uint32_t> dims, const std::vector<int32_t> &v) { put(name, 1, dims, v.data()); }
+    void u32(const std::string &name, std::vector<uint32_t> dims, const std::vector<uint32_t> &v) { put(name, 2, dims, v.data()); }
+    void close() {
+        fseek(f, 4, SEEK_SET);
+        fwrite(&count, 4, 1, f);
+        fclose(f);
+    }
+};
+
+static std::vector<float> Mat(const SquareMatrix<4> &m) {
+    std::vector<float> v(16);
+    for (int i = 0; i < 16; ++i) v[i] = m[i / 4][i % 4];
+    return v;
+}
+
+// spectra pool: 1 nm tables 395..705
+struct SpectraPool {
+    std::vector<float> values;
+    std::vector<uint32_t> interp;
+    int add(Spectrum s, uint32_t mode) {
+        for (int l = 395; l <= 705; ++l) values.push_back(s(Float(l)));
+        interp.push_back(mode);
+        return int(interp.size()) - 1;
+    }
+};
+
+static int countNodes(const LinearBVHNode *nodes) {
+    int maxIdx = 0;
+    std::vector<int> stack{0};
+    while (!stack.empty()) {
+        int i = stack.back();
+        stack.pop_back();
+        maxIdx = std::max(maxIdx, i);
+        if (nodes[i].nPrimitives == 0) {
+            stack.push_back(i + 1);
+            stack.push_back(nodes[i].secondChildOffset);
+        }
+    }
+    return maxIdx + 1;
+}
+
+int main(int argc, char **argv) {
+    if (argc < 3) die("usage: dumpscene_ref scene.pbrt out.b2rs");
+    PBRTOptions opt;
+    opt.quiet = true;
+    InitPBRT(opt);
+    BasicScene scene;
+    BasicSceneBuilder builder(&scene);
+    std::vector<std::string> files{argv[1]};
+    ParseFiles(&builder, files);
+
+    // ---- construction order of RenderCPU (cpu/render.cpp:25-55)
+    std::map<std::string, Medium> media = scene.CreateMedia();
+    NamedTextures textures = scene.CreateTextures();
+    std::map<int, pstd::vector<Light> *> shapeIndexToAreaLights;
+    std::vector<Light> lights = scene.CreateLights(textures, &shapeIndexToAreaLights);
+    std::map<std::string, pbrt::Material> namedMaterials;
+    std::vector<pbrt::Material> materials;
+    scene.CreateMaterials(textures, &namedMaterials, &materials);
+    std::string integratorName = scene.integrator.name;
+    ParameterDictionary integratorParams = scene.integrator.parameters;
+    Primitive accel = scene.CreateAggregate(textures, shapeIndexToAreaLights, media, namedMaterials, materials);
+    Camera camera = scene.GetCamera();
+    Film film = camera.GetFilm();
+    Sampler sampler = scene.GetSampler();
+
+    Writer w(argv[2]);
+    SpectraPool pool;
+
+    // ---- camera (perspective only for now)
+    if (!camera.Is<PerspectiveCamera>()) die("only the perspective camera is dumped so far");
+    const PerspectiveCamera *pc = camera.Cast<PerspectiveCamera>();
+    w.u32("camera_type", {1}, {0});
+    w.f32("camera_from_raster", {16}, Mat(pc->cameraFromRaster.GetMatrix()));
+    w.f32("render_from_camera", {16}, Mat(pc->cameraTransform.renderFromCamera.startTransform.GetMatrix()));
+    w.f32("camera_params", {2}, {pc->lensRadius, pc->focalDistance});
+
+    // ---- film (RGBFilm) and its sensor
+    if (!film.Is<RGBFilm>()) die("only the rgb film is dumped so far");
+    const RGBFilm *rf = film.Cast<RGBFilm>();
+    Bounds2i pb = rf->pixelBounds;
+    w.i32("film_ints", {6}, {pb.pMin.x, pb.pMin.y, pb.pMax.x, pb.pMax.y, rf->fullResolution.x, rf->fullResolution.y});
+    if (!rf->filter.Is<BoxFilter>()) die("only the box filter is dumped so far");
+    Vector2f fr = rf->filter.Radius();
+    w.f32("film_params", {4}, {fr.x, fr.y, rf->sensor->imagingRatio, rf->maxComponentValue});
+    std::vector<float> om(9);
+    for (int i = 0; i < 9; ++i) om[i] = rf->outputRGBFromSensorRGB[i / 3][i % 3];
+    w.f32("film_matrix", {9}, om);
+    int sr = pool.add(&rf->sensor->r_bar, 0), sg = pool.add(&rf->sensor->g_bar, 0), sb = pool.add(&rf->sensor->b_bar, 0);
+    w.i32("film_sensor", {3}, {sr, sg, sb});
+
+    // ---- sampler
+    if (sampler.Is<ZSobolSampler>()) {
+        const ZSobolSampler *zs = sampler.Cast<ZSobolSampler>();
+        w.i32("sampler", {6}, {0, 1 << zs->log2SamplesPerPixel, zs->seed, int(zs->randomize),
+                               zs->log2SamplesPerPixel, zs->nBase4Digits});
+    } else
+        die("only the zsobol sampler is dumped so far");
+
+    // ---- integrator parameters (cpu/integrators.cpp PathIntegrator::Create)
+    int maxDepth = integratorParams.GetOneInt("maxdepth", 5);
+    std::string ls = integratorParams.GetOneString("lightsampler", "bvh");
+    bool regularize = integratorParams.GetOneBool("regularize", false);
+    int lsId = ls == "uniform" ? 0 : (ls == "power" ? 1 : 2);
+    w.i32("integrator", {3}, {maxDepth, regularize ? 1 : 0, lsId});
+
+    // ---- geometry: walk the top-level BVH's ordered primitives (triangles only)
+    if (!accel.Is<BVHAggregate>()) die("top-level aggregate is not a BVH");
+    const BVHAggregate *bvh = accel.Cast<BVHAggregate>();
+    const auto &allMeshes = *Triangle::allMeshes;
+    size_t nMesh = allMeshes.size();
+    std::vector<int32_t> meshAttr(nMesh * 3, -1);
+    std::vector<const void *> meshMaterial(nMesh, nullptr);
+    std::map<const void *, int> materialId;
+    std::vector<pbrt::Material> materialList;
+    std::map<const void *, int> lightIndex;
+    for (size_t i = 0; i < lights.size(); ++i) lightIndex[lights[i].ptr()] = int(i);
+    std::vector<uint32_t> bvhPrims;
+    std::vector<int32_t> lightMeshTri(lights.size() * 2, -1);
+    for (const Primitive &p : bvh->primitives) {
+        Shape shape;
+        pbrt::Material mtl;
+        Light area;
+        if (const SimplePrimitive *sp = p.CastOrNullptr<SimplePrimitive>()) {
+            shape = sp->shape;
+            mtl = sp->material;
+        } else if (const GeometricPrimitive *gp = p.CastOrNullptr<GeometricPrimitive>()) {
+            shape = gp->shape;
+            mtl = gp->material;
+            area = gp->areaLight;
+            if (gp->alpha) die("alpha textures are not dumped");
+        } else
+            die("only triangle primitives are dumped so far");
+        if (!shape.Is<Triangle>()) die("only triangles are dumped so far");
+        const Triangle *t = shape.Cast<Triangle>();
+        int m = t->meshIndex;
+        bvhPrims.insert(bvhPrims.end(), {0u, uint32_t(m), uint32_t(t->triIndex)});
+        if (!materialId.count(mtl.ptr())) {
+            materialId[mtl.ptr()] = int(materialList.size());
+            materialList.push_back(mtl);
+        }
+        meshAttr[3 * m + 0] = mtl ? materialId[mtl.ptr()] : -1;
+        meshAttr[3 * m + 2] = (allMeshes[m]->reverseOrientation ^ allMeshes[m]->transformSwapsHandedness) ? 1 : 0;
+        if (area) {
+            int li = lightIndex.at(area.ptr());
+            lightMeshTri[2 * li] = m;
+            lightMeshTri[2 * li + 1] = t->triIndex;
+            int first = li - t->triIndex;
+            if (meshAttr[3 * m + 1] != -1 && meshAttr[3 * m + 1] != first) die("area lights of a mesh are not consecutive");
+            meshAttr[3 * m + 1] = first;
+        }
+    }
+    // Meshes that no primitive of the aggregate refers to (the private shape copies the area
+    // lights keep) are left out; the rest are renumbered densely.
+    std::vector<int> meshRemap(nMesh, -1);
+    {
+        std::vector<char> used(nMesh, 0);
+        for (size_t i = 0; i < bvhPrims.size(); i += 3) used[bvhPrims[i + 1]] = 1;
+        int next = 0;
+        for (size_t m = 0; m < nMesh; ++m)
+            if (used[m]) meshRemap[m] = next++;
+        std::vector<int32_t> attr2(size_t(next) * 3);
+        for (size_t m = 0; m < nMesh; ++m)
+            if (used[m]) memcpy(&attr2[3 * meshRemap[m]], &meshAttr[3 * m], 12);
+        meshAttr.swap(attr2);
+        for (size_t i = 0; i < bvhPrims.size(); i += 3) bvhPrims[i + 1] = meshRemap[bvhPrims[i + 1]];
+        for (size_t i = 0; i < lightMeshTri.size(); i += 2)
+            if (lightMeshTri[i] >= 0) lightMeshTri[i] = meshRemap[lightMeshTri[i]];
+    }
+    size_t nMeshAll = nMesh;
+    nMesh = meshAttr.size() / 3;
+    std::vector<uint32_t> nv, nt;
+    std::vector<float> P;
+    std::vector<int32_t> idx;
+    for (size_t m = 0; m < nMeshAll; ++m) {
+        if (meshRemap[m] < 0) continue;
+        const TriangleMesh *mesh = allMeshes[m];
+        if (mesh->n || mesh->uv || mesh->s) fprintf(stderr, "dumpscene_ref: note: per-vertex n/uv/s of mesh %zu ignored\n", m);
+        nv.push_back(mesh->nVertices);
+        nt.push_back(mesh->nTriangles);
+        for (int i = 0; i < mesh->nVertices; ++i) P.insert(P.end(), {mesh->p[i].x, mesh->p[i].y, mesh->p[i].z});
+        idx.insert(idx.end(), mesh->vertexIndices, mesh->vertexIndices + 3 * mesh->nTriangles);
+    }
+    w.u32("mesh_nverts", {uint32_t(nMesh)}, nv);
+    w.u32("mesh_ntris", {uint32_t(nMesh)}, nt);
+    w.f32("P", {uint32_t(P.size() / 3), 3}, P);
+    w.i32("indices", {uint32_t(idx.size() / 3), 3}, idx);
+    w.i32("mesh_attr", {uint32_t(nMesh), 3}, meshAttr);
+    int nNodes = countNodes(bvh->nodes);
+    std::vector<uint32_t> nodeWords(size_t(nNodes) * 8);
+    memcpy(nodeWords.data(), bvh->nodes, size_t(nNodes) * 32);
+    w.u32("bvh_nodes", {uint32_t(nNodes), 8}, nodeWords);
+    w.u32("bvh_prims", {uint32_t(bvhPrims.size() / 3), 3}, bvhPrims);
+
+    // ---- materials
+    std::vector<int32_t> matI;
+    std::vector<float> matF;
+    for (pbrt::Material mtl : materialList) {
+        int32_t rec[5] = {-1, -1, -1, -1, -1};
+        float prm[8] = {0};
+        if (!mtl) {
+            rec[0] = -1;
+        } else if (const DiffuseMaterial *dm = mtl.CastOrNullptr<DiffuseMaterial>()) {
+            const SpectrumConstantTexture *ct = dm->reflectance.CastOrNullptr<SpectrumConstantTexture>();
+            if (!ct) die("only constant reflectance textures are dumped so far");
+            rec[0] = 0;
+            rec[1] = pool.add(ct->value, 1);
+        } else
+            die("only diffuse materials are dumped so far");
+        matI.insert(matI.end(), rec, rec + 5);
+        matF.insert(matF.end(), prm, prm + 8);
+    }
+    w.i32("materials_i", {uint32_t(materialList.size()), 5}, matI);
+    w.f32("materials_f", {uint32_t(materialList.size()), 8}, matF);
+
+    // ---- lights + the power sampler's alias table (lightsamplers.cpp:76-96, util/sampling.cpp:562-617)
+    PowerLightSampler pls(pstd::span<const Light>(lights.data(), lights.size()), Allocator());
+    std::vector<int32_t> lightI;
+    std::vector<float> lightF;
+    std::map<const void *, int> lemitId;
+    for (size_t i = 0; i < lights.size(); ++i) {
+        const DiffuseAreaLight *al = lights[i].CastOrNullptr<DiffuseAreaLight>();
+        if (!al) die("only diffuse area lights are dumped so far");
+        if (al->image) die("image area lights are not dumped");
+        if (!lemitId.count(al->Lemit)) lemitId[al->Lemit] = pool.add(al->Lemit, 0);
+        int m = lightMeshTri[2 * i], tri = lightMeshTri[2 * i + 1];
+        if (m < 0) die("area light without a triangle in the aggregate");
+        const auto &bin = pls.aliasTable.bins[i];
+        lightI.insert(lightI.end(), {m, tri, lemitId[al->Lemit], al->twoSided ? 1 : 0, bin.alias, meshAttr[3 * m + 2]});
+        lightF.insert(lightF.end(), {al->scale, al->cosFalloffEnd, al->tanFalloffEnd, al->normalize_falloffEnd, bin.q, bin.p});
+    }
+    w.i32("lights_i", {uint32_t(lights.size()), 6}, lightI);
+    w.f32("lights_f", {uint32_t(lights.size()), 6}, lightF);
+
+    w.f32("spectra_values", {uint32_t(pool.interp.size()), 311}, pool.values);
+    w.u32("spectra_interp", {uint32_t(pool.interp.size())}, pool.interp);
+    w.close();
+    printf("{\"meshes\": %zu, \"triangles\": %zu, \"lights\": %zu, \"materials\": %zu, \"spectra\": %zu}\n", nMesh,
+           idx.size() / 3, lights.size(), materialList.size(), pool.interp.size());
+    fflush(stdout);
+    _Exit(0);
+}

@@ -66,7 +66,7 @@ LIB := $(OUT)/libpbrt_ref.a
 # dumps, never EXR; calling it would fault.
 LDFLAGS := -pthread -no-pie -Wl,--unresolved-symbols=ignore-all
 
-all: $(OUT)/pbrt_ref $(OUT)/raycast_ref
+all: $(OUT)/pbrt_ref $(OUT)/raycast_ref $(OUT)/dumpscene_ref
 
 $(GEN)/soac: $(REF)/src/pbrt/cmd/soac.cpp
 	@mkdir -p $(GEN)
@@ -134,6 +134,8 @@ $(OUT)/pbrt_ref: $(REF)/src/pbrt/cmd/pbrt.cpp $(LIB)
 # BVHAggregate::nodes / primitives (cpu/aggregates.h:66-69); layouts are
 # unchanged so it links against the normally-compiled library.
 $(OUT)/raycast_ref: oracle/raycast_ref.cpp $(LIB)
+	$(CXX) $(CXXFLAGS) $< $(LIB) $(LDFLAGS) -o $@
+$(OUT)/dumpscene_ref: oracle/dumpscene_ref.cpp $(LIB)
 	$(CXX) $(CXXFLAGS) $< $(LIB) $(LDFLAGS) -o $@
 
 .PHONY: all

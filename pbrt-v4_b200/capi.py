@@ -116,3 +116,53 @@ def bvh2_build(boxes, max_prims_in_node=4):
     check(lib().b200pt_bvh2_build(fptr(boxes), n, int(max_prims_in_node), nodes.ctypes.data,
                                   C.byref(nn), order.ctypes.data_as(C.POINTER(C.c_uint32))))
     return nodes[:nn.value].copy(), order
+
+
+# ------------------------------------------------------------------ render path structs
+class Spectrum(C.Structure):
+    _fields_ = [("interp", C.c_uint32), ("values", C.c_float * 311)]
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("spectrum", C.c_int32 * 4), ("params", C.c_float * 8)]
+
+
+class Light(C.Structure):
+    _fields_ = [("mesh", C.c_uint32), ("tri", C.c_uint32), ("spectrum", C.c_int32), ("scale", C.c_float),
+                ("two_sided", C.c_uint32), ("cos_falloff_end", C.c_float), ("tan_falloff_end", C.c_float),
+                ("normalize_falloff_end", C.c_float), ("alias_q", C.c_float), ("alias_p", C.c_float),
+                ("alias", C.c_int32)]
+
+
+class MeshAttr(C.Structure):
+    _fields_ = [("material", C.c_int32), ("light_first", C.c_int32), ("flip_normal", C.c_uint32)]
+
+
+class RenderDesc(C.Structure):
+    _fields_ = [("camera_type", C.c_uint32), ("camera_from_raster", C.c_float * 16),
+                ("render_from_camera", C.c_float * 16), ("lens_radius", C.c_float), ("focal_distance", C.c_float),
+                ("film_type", C.c_uint32), ("pixel_bounds", C.c_int32 * 4), ("full_resolution", C.c_int32 * 2),
+                ("filter_radius", C.c_float * 2), ("imaging_ratio", C.c_float), ("max_component_value", C.c_float),
+                ("output_rgb_from_sensor_rgb", C.c_float * 9), ("sensor_spectrum", C.c_int32 * 3),
+                ("sampler_type", C.c_uint32), ("samples_per_pixel", C.c_int32), ("seed", C.c_int32),
+                ("randomize", C.c_uint32), ("max_depth", C.c_int32), ("regularize", C.c_uint32),
+                ("light_sampler", C.c_uint32), ("n_spectra", C.c_uint32), ("n_materials", C.c_uint32),
+                ("n_lights", C.c_uint32), ("n_meshes", C.c_uint32), ("spectra", C.POINTER(Spectrum)),
+                ("materials", C.POINTER(Material)), ("lights", C.POINTER(Light)), ("meshes", C.POINTER(MeshAttr))]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("kernel_launches", C.c_uint32), ("gpu_ms", C.c_float)]
+
+
+SYMBOLS.update({
+    "b200pt_render_create": (C.c_int, [C.c_void_p, C.POINTER(RenderDesc), C.POINTER(C.c_void_p)]),
+    "b200pt_render_destroy": (C.c_int, [C.c_void_p]),
+    "b200pt_render_run": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
+    "b200pt_film_clear": (C.c_int, [C.c_void_p]),
+    "b200pt_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
+    "b200pt_film_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "b200pt_film_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "b200pt_render_get_stats": (C.c_int, [C.c_void_p, C.POINTER(RenderStats)]),
+})

@@ -1,0 +1,130 @@
+// render_host.cpp - validation + flattening of the render description (see render_host.h).
+#include "render_host.h"
+
+#include <cmath>
+#include <cstring>
+#include <map>
+
+namespace b200pt {
+
+static int Log2Int(uint32_t v) {
+    int l = 0;
+    while (v >>= 1) ++l;
+    return l;
+}
+static uint32_t RoundUpPow2(uint32_t v) {
+    uint32_t p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t nSceneMeshes, RenderHost &out,
+                      std::string &err) {
+    auto bad = [&](const char *m) {
+        err = m;
+        return B200PT_ERR_INVALID;
+    };
+    if (!d) return bad("null render description");
+    if (d->camera_type != 0) return bad("unsupported camera type");
+    if (d->film_type != 0) return bad("unsupported film type");
+    if (d->sampler_type != 0) return bad("unsupported sampler type");
+    if (d->light_sampler > 1) return bad("unsupported light sampler (uniform and power are implemented)");
+    if (d->n_meshes != nSceneMeshes) return bad("mesh attribute count differs from the geometry scene");
+    if ((d->n_spectra && !d->spectra) || (d->n_materials && !d->materials) || (d->n_lights && !d->lights) ||
+        (d->n_meshes && !d->meshes))
+        return bad("null table in render description");
+    int w = d->pixel_bounds[2] - d->pixel_bounds[0], h = d->pixel_bounds[3] - d->pixel_bounds[1];
+    if (w <= 0 || h <= 0) return bad("empty pixel bounds");
+    if (d->samples_per_pixel < 1 || d->max_depth < 0) return bad("bad sampler / integrator parameters");
+    auto specOk = [&](int32_t s) { return s >= 0 && uint32_t(s) < d->n_spectra; };
+    for (int c = 0; c < 3; ++c)
+        if (!specOk(d->sensor_spectrum[c])) return bad("sensor spectrum index out of range");
+
+    RenderSceneDev &rs = out.rs;
+    rs.camera.type = 0;
+    std::memcpy(rs.camera.cameraFromRaster, d->camera_from_raster, 64);
+    std::memcpy(rs.camera.renderFromCamera, d->render_from_camera, 64);
+    rs.camera.lensRadius = d->lens_radius;
+    rs.camera.focalDistance = d->focal_distance;
+    rs.film.type = 0;
+    rs.film.x0 = d->pixel_bounds[0];
+    rs.film.y0 = d->pixel_bounds[1];
+    rs.film.x1 = d->pixel_bounds[2];
+    rs.film.y1 = d->pixel_bounds[3];
+    rs.film.fullResX = d->full_resolution[0];
+    rs.film.fullResY = d->full_resolution[1];
+    rs.film.filterType = 0;
+    rs.film.filterRadiusX = d->filter_radius[0];
+    rs.film.filterRadiusY = d->filter_radius[1];
+    rs.film.imagingRatio = d->imaging_ratio;
+    rs.film.maxComponentValue = d->max_component_value;
+    std::memcpy(rs.film.outputRGBFromSensorRGB, d->output_rgb_from_sensor_rgb, 36);
+    for (int c = 0; c < 3; ++c) rs.film.sensorSpectrum[c] = d->sensor_spectrum[c];
+    // ZSobolSampler constructor (samplers.h:228-238)
+    rs.sampler.type = 0;
+    rs.sampler.samplesPerPixel = d->samples_per_pixel;
+    rs.sampler.seed = d->seed;
+    rs.sampler.randomize = d->randomize;
+    rs.sampler.log2Spp = Log2Int(uint32_t(d->samples_per_pixel));
+    int res = int(RoundUpPow2(uint32_t(std::max(d->full_resolution[0], d->full_resolution[1]))));
+    rs.sampler.nBase4Digits = Log2Int(uint32_t(res)) + (rs.sampler.log2Spp + 1) / 2;
+    rs.integrator.maxDepth = d->max_depth;
+    rs.integrator.regularize = d->regularize;
+    rs.integrator.lightSampler = d->light_sampler;
+
+    out.spectra.resize(d->n_spectra);
+    for (uint32_t i = 0; i < d->n_spectra; ++i) {
+        out.spectra[i].interp = d->spectra[i].interp;
+        std::memcpy(out.spectra[i].values, d->spectra[i].values, sizeof(float) * kSpecTable);
+    }
+    out.materials.resize(d->n_materials);
+    for (uint32_t i = 0; i < d->n_materials; ++i) {
+        const b200pt_material &m = d->materials[i];
+        if (m.type != B200PT_MAT_DIFFUSE) return bad("unsupported material type (diffuse is implemented)");
+        if (!specOk(m.spectrum[0])) return bad("material spectrum index out of range");
+        out.materials[i].type = m.type;
+        std::memcpy(out.materials[i].spectrum, m.spectrum, 16);
+        std::memcpy(out.materials[i].params, m.params, 32);
+    }
+    // (mesh, tri) -> primitive slot of the geometry scene
+    std::map<uint64_t, uint32_t> slotOf;
+    for (uint32_t s = 0; s < hs.prims.size(); ++s)
+        if (hs.prims[s].mesh < kInstanceTag) slotOf[(uint64_t(hs.prims[s].mesh) << 32) | hs.prims[s].tri] = s;
+    out.meshes.resize(d->n_meshes);
+    for (uint32_t i = 0; i < d->n_meshes; ++i) {
+        const b200pt_mesh_attr &m = d->meshes[i];
+        if (m.material >= int32_t(d->n_materials)) return bad("mesh material index out of range");
+        if (m.light_first >= int32_t(d->n_lights)) return bad("mesh light index out of range");
+        out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, 0};
+    }
+    out.lights.resize(d->n_lights);
+    for (uint32_t i = 0; i < d->n_lights; ++i) {
+        const b200pt_light &l = d->lights[i];
+        auto it = slotOf.find((uint64_t(l.mesh) << 32) | l.tri);
+        if (it == slotOf.end()) return bad("light refers to a triangle that is not in the scene");
+        if (!specOk(l.spectrum)) return bad("light spectrum index out of range");
+        if (l.alias >= int32_t(d->n_lights)) return bad("alias index out of range");
+        LightDev &o = out.lights[i];
+        o.type = 0;
+        o.slot = it->second;
+        o.spectrum = l.spectrum;
+        o.scale = l.scale;
+        o.twoSided = l.two_sided;
+        o.cosFalloffEnd = l.cos_falloff_end;
+        o.tanFalloffEnd = l.tan_falloff_end;
+        o.normalizeFalloffEnd = l.normalize_falloff_end;
+        o.aliasQ = l.alias_q;
+        o.aliasP = l.alias_p;
+        o.alias = l.alias;
+        o.flipNormal = l.mesh < d->n_meshes ? d->meshes[l.mesh].flip_normal : 0;
+    }
+    rs.nSpectra = d->n_spectra;
+    rs.nMaterials = d->n_materials;
+    rs.nLights = d->n_lights;
+    rs.nMeshes = d->n_meshes;
+    out.width = w;
+    out.height = h;
+    return B200PT_OK;
+}
+
+}  // namespace b200pt

@@ -1,0 +1,25 @@
+// render_host.h - b200pt_render_desc -> the POD tables of render_types.h (host copies; the API
+// uploads them, tests/native/rendercheck.cpp uses them in place).  Pure host code.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "../../include/b200pt.h"
+#include "render_types.h"
+#include "scene_host.h"
+
+namespace b200pt {
+
+struct RenderHost {
+    RenderSceneDev rs{};  // pointer members are filled by whoever owns the storage (host or device)
+    std::vector<SpectrumTable> spectra;
+    std::vector<MaterialDev> materials;
+    std::vector<LightDev> lights;
+    std::vector<MeshAttrDev> meshes;
+    int width = 0, height = 0;
+};
+
+int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t nSceneMeshes, RenderHost &out,
+                      std::string &err);
+
+}  // namespace b200pt

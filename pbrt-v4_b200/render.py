@@ -1,0 +1,160 @@
+"""Host side of the render path: a RenderScene (the flat tables a pbrt host adaptor hands over, e.g.
+a `.b2rs` dump) marshalled into include/b200pt.h structs, and B200Renderer, the Python mirror of
+RenderWavefront (reference wavefront/wavefront.cpp:14-70): create -> run sample ranges -> read film."""
+import ctypes as C
+
+import numpy as np
+
+from . import capi, scenes
+from .aggregate import B200Aggregate
+
+
+class RenderScene:
+    """Geometry + render tables.  `d` is a dict of arrays with the .b2rs names (scenes.load_b2rs)."""
+
+    def __init__(self, d):
+        self.d = d
+        nv, nt = d["mesh_nverts"].astype(np.int64), d["mesh_ntris"].astype(np.int64)
+        vo, to = np.concatenate([[0], np.cumsum(nv)]), np.concatenate([[0], np.cumsum(nt)])
+        self.geometry = scenes.Scene([scenes.Mesh(d["P"][vo[i]:vo[i + 1]], d["indices"][to[i]:to[i + 1]])
+                                      for i in range(len(nv))])
+        self.bvh = None
+        if "bvh_nodes" in d:
+            nodes = np.ascontiguousarray(d["bvh_nodes"]).view(capi.NODE32_DTYPE).reshape(-1)
+            self.bvh = [(-1, nodes, d["bvh_prims"])]
+
+    @classmethod
+    def load(cls, path):
+        return cls(scenes.load_b2rs(path))
+
+    @property
+    def resolution(self):
+        b = self.d["film_ints"]
+        return int(b[2] - b[0]), int(b[3] - b[1])
+
+    @property
+    def spp(self):
+        return int(self.d["sampler"][1])
+
+    def desc(self, keep):
+        """-> capi.RenderDesc (arrays it points to are appended to `keep`)."""
+        d = self.d
+        r = capi.RenderDesc()
+        r.camera_type = int(d["camera_type"][0])
+        r.camera_from_raster[:] = [float(x) for x in d["camera_from_raster"]]
+        r.render_from_camera[:] = [float(x) for x in d["render_from_camera"]]
+        r.lens_radius, r.focal_distance = float(d["camera_params"][0]), float(d["camera_params"][1])
+        r.film_type = 0
+        r.pixel_bounds[:] = [int(x) for x in d["film_ints"][:4]]
+        r.full_resolution[:] = [int(x) for x in d["film_ints"][4:6]]
+        r.filter_radius[:] = [float(x) for x in d["film_params"][:2]]
+        r.imaging_ratio, r.max_component_value = float(d["film_params"][2]), float(d["film_params"][3])
+        r.output_rgb_from_sensor_rgb[:] = [float(x) for x in d["film_matrix"]]
+        r.sensor_spectrum[:] = [int(x) for x in d["film_sensor"]]
+        s = d["sampler"]
+        r.sampler_type, r.samples_per_pixel, r.seed, r.randomize = int(s[0]), int(s[1]), int(s[2]), int(s[3])
+        r.max_depth, r.regularize, r.light_sampler = (int(x) for x in d["integrator"])
+        ns, nm, nl, nme = len(d["spectra_interp"]), len(d["materials_i"]), len(d["lights_i"]), len(d["mesh_attr"])
+        spectra = (capi.Spectrum * max(ns, 1))()
+        for i in range(ns):
+            spectra[i].interp = int(d["spectra_interp"][i])
+            C.memmove(spectra[i].values, np.ascontiguousarray(d["spectra_values"][i], np.float32).ctypes.data, 311 * 4)
+        mats = (capi.Material * max(nm, 1))()
+        for i in range(nm):
+            mi = d["materials_i"][i]
+            mats[i].type = int(mi[0]) if mi[0] >= 0 else 0
+            mats[i].spectrum[:] = [int(x) for x in mi[1:5]]
+            mats[i].params[:] = [float(x) for x in d["materials_f"][i]]
+        lights = (capi.Light * max(nl, 1))()
+        for i in range(nl):
+            li, lf = d["lights_i"][i], d["lights_f"][i]
+            lights[i] = capi.Light(int(li[0]), int(li[1]), int(li[2]), float(lf[0]), int(li[3]), float(lf[1]),
+                                   float(lf[2]), float(lf[3]), float(lf[4]), float(lf[5]), int(li[4]))
+        meshes = (capi.MeshAttr * max(nme, 1))()
+        for i in range(nme):
+            a = d["mesh_attr"][i]
+            meshes[i] = capi.MeshAttr(int(a[0]), int(a[1]), int(max(a[2], 0)))
+        r.n_spectra, r.n_materials, r.n_lights, r.n_meshes = ns, nm, nl, nme
+        r.spectra, r.materials, r.lights, r.meshes = spectra, mats, lights, meshes
+        keep += [spectra, mats, lights, meshes]
+        return r
+
+
+def scene_desc(geometry, bvh, keep):
+    """scenes.Scene (+ optional host BVH) -> capi.SceneDesc."""
+    meshes = (capi.Mesh * max(1, len(geometry.meshes)))()
+    for k, m in enumerate(geometry.meshes):
+        p, idx = np.ascontiguousarray(m.p, np.float32), np.ascontiguousarray(m.indices, np.int32)
+        keep += [p, idx]
+        meshes[k] = capi.Mesh(int(m.object), p.shape[0], idx.shape[0], capi.fptr(p),
+                              idx.ctypes.data_as(C.POINTER(C.c_int32)))
+    barr = (capi.BVH2 * max(1, len(bvh) if bvh else 1))()
+    nb = 0
+    if bvh:
+        for k, (obj, nodes, prims) in enumerate(bvh):
+            nodes, prims = np.ascontiguousarray(nodes), np.ascontiguousarray(prims, np.uint32).reshape(-1, 3)
+            keep += [nodes, prims]
+            barr[k] = capi.BVH2(int(obj), nodes.shape[0], prims.shape[0], nodes.ctypes.data,
+                                prims.ctypes.data_as(C.POINTER(C.c_uint32)))
+        nb = len(bvh)
+    insts = (capi.Instance * 1)()
+    keep += [meshes, barr, insts]
+    return capi.SceneDesc(len(geometry.meshes), meshes, 0, insts, nb, barr, 0)
+
+
+class B200Renderer:
+    """create -> render(sample range) -> image, all on the GPU through libb200pt.so."""
+
+    def __init__(self, rscene, device=0, stream=None, use_host_bvh=False):
+        self.rscene = rscene
+        self.agg = B200Aggregate(rscene.geometry, device=device, stream=stream,
+                                 bvhs=rscene.bvh if use_host_bvh else None)
+        self._L = capi.lib()
+        self._r = C.c_void_p()
+        keep = []
+        desc = rscene.desc(keep)
+        capi.check(self._L.b200pt_render_create(self.agg._scene, C.byref(desc), C.byref(self._r)), self.agg._ctx)
+        self.width, self.height = rscene.resolution
+
+    def render(self, first_sample=0, n_samples=None, stride=1):
+        n = self.rscene.spp if n_samples is None else n_samples
+        capi.check(self._L.b200pt_render_run(self._r, int(first_sample), int(n), int(stride)), self.agg._ctx)
+
+    def clear(self):
+        capi.check(self._L.b200pt_film_clear(self._r), self.agg._ctx)
+
+    def film(self):
+        out = np.empty((self.height, self.width, 4), dtype=np.float64)
+        capi.check(self._L.b200pt_film_read(self._r, out.ctypes.data_as(C.POINTER(C.c_double))), self.agg._ctx)
+        return out
+
+    def film_device_ptr(self):
+        p, n = C.c_void_p(), C.c_uint64()
+        capi.check(self._L.b200pt_film_device_ptr(self._r, C.byref(p), C.byref(n)), self.agg._ctx)
+        return p.value, n.value
+
+    def image(self):
+        out = np.empty((self.height, self.width, 3), dtype=np.float32)
+        capi.check(self._L.b200pt_film_image(self._r, out.ctypes.data_as(C.POINTER(C.c_float))), self.agg._ctx)
+        return out
+
+    def stats(self):
+        s = capi.RenderStats()
+        capi.check(self._L.b200pt_render_get_stats(self._r, C.byref(s)), self.agg._ctx)
+        return {k: getattr(s, k) for k, _ in capi.RenderStats._fields_}
+
+    def sync(self):
+        self.agg.sync()
+
+    def close(self):
+        if self._r:
+            self._L.b200pt_render_destroy(self._r)
+            self._r = C.c_void_p()
+        self.agg.close()
+
+
+def film_to_image(film_rgbw, matrix):
+    """RGBFilm::GetPixelRGB (film.h:261-277): rgbSum / weightSum, then outputRGBFromSensorRGB."""
+    w = film_rgbw[..., 3:4]
+    rgb = np.where(w != 0, film_rgbw[..., :3] / np.where(w != 0, w, 1), film_rgbw[..., :3])
+    return (rgb.astype(np.float32) @ np.asarray(matrix, np.float32).reshape(3, 3).T).astype(np.float32)

@@ -241,3 +241,57 @@ def camera_rays(width, height, eye, look, up=(0, 1, 0), fov_deg=40.0, spp=1, see
     rays = np.empty((xs.shape[0], 7), dtype=np.float32)
     rays[:, 0:3], rays[:, 3:6], rays[:, 6] = eye, d, np.inf
     return rays
+
+
+# ------------------------------------------------------------------ .pbrt text for the reference (config 1)
+
+def _mesh_pbrt(m):
+    idx = " ".join(str(int(i)) for i in m.indices.reshape(-1))
+    pts = " ".join(repr(float(x)) for x in m.p.reshape(-1))
+    return f'Shape "trianglemesh" "integer indices" [{idx}] "point3 P" [{pts}]'
+
+
+def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0):
+    """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
+    ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
+    sc = cornell_box()
+    white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
+    colours = [white, white, white, red, green, None, white, white]
+    lines = [
+        'LookAt 0.5 0.5 -1.4  0.5 0.5 0.5  0 1 0',
+        'Camera "perspective" "float fov" 39.3',
+        f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
+        f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "{lightsampler}"',
+        'PixelFilter "box"',
+        f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false',
+        'WorldBegin',
+    ]
+    for m, c in zip(sc.meshes, colours):
+        lines.append('AttributeBegin')
+        if c is None:
+            lines.append('  AreaLightSource "diffuse" "rgb L" [17 12 4]')
+            lines.append('  Material "diffuse" "rgb reflectance" [0 0 0]')
+        else:
+            lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
+        lines.append('  ' + _mesh_pbrt(m))
+        lines.append('AttributeEnd')
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return sc
+
+
+def load_b2rs(path):
+    """Reads the named-array container written by a host adaptor (oracle/dumpscene_ref.cpp is the
+    test-side one): 'B2RS', u32 count, {u32 nameLen, name, u32 dtype, u32 ndim, u32 dims[], data}."""
+    out = {}
+    with open(path, "rb") as f:
+        magic, count = np.fromfile(f, dtype="<u4", count=2)
+        assert magic == 0x53523242, "not a .b2rs file"
+        for _ in range(int(count)):
+            nl = int(np.fromfile(f, dtype="<u4", count=1)[0])
+            name = f.read(nl).decode()
+            dtype, nd = (int(x) for x in np.fromfile(f, dtype="<u4", count=2))
+            dims = [int(x) for x in np.fromfile(f, dtype="<u4", count=nd)]
+            n = int(np.prod(dims)) if dims else 1
+            out[name] = np.fromfile(f, dtype=["<f4", "<i4", "<u4"][dtype], count=n).reshape(dims)
+    return out

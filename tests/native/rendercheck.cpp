@@ -1,0 +1,123 @@
+// tests/native/rendercheck.cpp - TEST-ONLY shared library that runs the render path's host+device
+// functions (pbrt-v4_b200/csrc/render_*.h) on the CPU, one path at a time, with the PairNode walk of
+// traverse_persist.cu for the rays.  Lets the whole pipeline be compared with pbrt_ref in the
+// GPU-less container.  Not part of libb200pt.so; the product never calls it.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../pbrt-v4_b200/csrc/render_core.h"
+#include "../../pbrt-v4_b200/csrc/render_host.h"
+#include "../../pbrt-v4_b200/csrc/scene_host.h"
+
+using namespace b200pt;
+
+namespace {
+
+struct E {
+    int ref;
+    float t;
+};
+
+// closest hit -> internal record {slot, t, b0, b1, b2, 0}; any = occlusion only
+bool Trace(const HostScene &hs, V3 o, V3 d, float tMax, bool any, uint32_t hit[6]) {
+    RayCtx r;
+    RaySetup(r, o.x, o.y, o.z, d.x, d.y, d.z);
+    E stack[128];
+    int sp = 0, cur = 0, best = -1;
+    float bb0 = 0, bb1 = 0, bb2 = 0;
+    bool done = false;
+    auto popNext = [&]() {
+        done = true;
+        while (sp > 0) {
+            E e = stack[--sp];
+            if (e.t < tMax) {
+                cur = e.ref;
+                done = false;
+                break;
+            }
+        }
+    };
+    if (SlabTest(r, hs.bounds, hs.bounds + 3, tMax)) cur = hs.rootRef; else done = true;
+    while (!done) {
+        if (cur >= 0) {
+            const PairNode &pn = hs.pairs[cur];
+            float t0, t1;
+            bool h0 = SlabCore(r, pn.box0, pn.box0 + 3, t0), h1 = SlabCore(r, pn.box1, pn.box1 + 3, t1);
+            bool neg = r.neg[pn.axis] != 0;
+            int nearRef = neg ? pn.ref1 : pn.ref0, farRef = neg ? pn.ref0 : pn.ref1;
+            float tNear = neg ? t1 : t0, tFar = neg ? t0 : t1;
+            bool hNear = (neg ? h1 : h0) && (tNear < tMax), hFar = neg ? h0 : h1;
+            if (hFar) stack[sp++] = E{farRef, tFar};
+            if (hNear) cur = nearRef; else popNext();
+        } else {
+            int slot = ~cur, cnt = int(hs.prims[slot].flags);
+            for (int k = 0; k < cnt; ++k, ++slot) {
+                const PrimSlot &s = hs.prims[slot];
+                float t, b0, b1, b2;
+                if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
+                    if (any) return true;
+                    tMax = t; best = slot; bb0 = b0; bb1 = b1; bb2 = b2;
+                }
+            }
+            popNext();
+        }
+    }
+    if (any) return false;
+    if (best < 0) { hit[0] = kMissTag; return false; }
+    hit[0] = uint32_t(best);
+    memcpy(&hit[1], &tMax, 4); memcpy(&hit[2], &bb0, 4); memcpy(&hit[3], &bb1, 4); memcpy(&hit[4], &bb2, 4);
+    hit[5] = 0;
+    return true;
+}
+
+}  // namespace
+
+// rgbw: 4 doubles per pixel (rgbSum, weightSum), row major.  Returns 0 or an error code; err text in msg.
+extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_desc *rd, int firstSample,
+                               int nSamples, int stride, double *rgbw, char *msg, int msgLen, int nThreads) {
+    HostScene hs;
+    RenderHost rh;
+    std::string err;
+    int rc = AssembleScene(sd, hs, err);
+    if (rc == 0) rc = BuildRenderTables(rd, hs, sd->n_meshes, rh, err);
+    if (rc != 0) {
+        snprintf(msg, msgLen, "%s", err.c_str());
+        return rc;
+    }
+    RenderSceneDev rs = rh.rs;
+    rs.spectra = rh.spectra.data();
+    rs.materials = rh.materials.data();
+    rs.lights = rh.lights.data();
+    rs.meshes = rh.meshes.data();
+    rs.prims = hs.prims.data();
+    const int W = rh.width, H = rh.height;
+    if (nThreads < 1) nThreads = 1;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nThreads; ++t)
+        pool.emplace_back([&, t]() {
+            for (int y = t; y < H; y += nThreads)
+                for (int x = 0; x < W; ++x)
+                    for (int k = 0; k < nSamples; ++k) {
+                        PathRegs p;
+                        GenerateCameraPath(rs, p, rs.film.x0 + x, rs.film.y0 + y, firstSample + k * stride);
+                        bool occluded = false;
+                        // depth loop: one closest-hit + one shadow ray per vertex, as the kernels do
+                        while (p.flags & PF_ALIVE) {
+                            uint32_t hit[6] = {kMissTag, 0, 0, 0, 0, 0};
+                            Trace(hs, p.rayO, p.rayD, p.rayTMax, false, hit);
+                            ShadeVertex(rs, p, hit, occluded);
+                            occluded = false;
+                            if (p.flags & PF_SHADOW_PENDING) occluded = Trace(hs, p.shO, p.shD, p.shTMax, true, nullptr);
+                        }
+                        float out[4];
+                        FinishPath(rs, p, occluded, out);
+                        double *px = rgbw + 4 * (size_t(y) * W + x);
+                        for (int c = 0; c < 4; ++c) px[c] += out[c];
+                    }
+        });
+    for (auto &th : pool) th.join();
+    return 0;
+}
