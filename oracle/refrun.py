@@ -69,3 +69,42 @@ class RefScene:
                 prims = np.fromfile(f, dtype="<u4", count=3 * npr).reshape(-1, 3)
                 trees.append((obj, nodes, prims))
         return trees
+
+
+# ------------------------------------------------------------------ whole-image reference (pbrt_ref)
+DUMPSCENE = os.path.join(REF_DIR, "dumpscene_ref")
+
+
+def render_available():
+    return os.access(PBRT, os.X_OK) and os.access(DUMPSCENE, os.X_OK)
+
+
+def read_pfm(path):
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"PF"
+        w, h = map(int, f.readline().split())
+        scale = float(f.readline())
+        a = np.fromfile(f, "<f4" if scale < 0 else ">f4").reshape(h, w, 3)
+    return np.ascontiguousarray(a[::-1])  # PFM rows go bottom-up
+
+
+def render(pbrt_file, out_pfm, nthreads=None, timeout=3600):
+    """Runs the reference CPU renderer (its own main: cmd/pbrt.cpp) on a .pbrt file whose Film
+    writes `out_pfm`; returns (image, seconds)."""
+    import time
+    args = [PBRT, "--quiet"] + (["--nthreads", str(nthreads)] if nthreads else []) + [pbrt_file]
+    t = time.time()
+    r = subprocess.run(args, capture_output=True, text=True, timeout=timeout, cwd=os.path.dirname(pbrt_file))
+    dt = time.time() - t
+    if r.returncode != 0:
+        raise RuntimeError(f"pbrt_ref failed ({r.returncode}): {r.stderr[-2000:]}")
+    return read_pfm(out_pfm), dt
+
+
+def dump_scene(pbrt_file, out_b2rs):
+    """Scene tables as the reference's own parser + object creation produced them (dumpscene_ref.cpp)."""
+    r = subprocess.run([DUMPSCENE, pbrt_file, out_b2rs], capture_output=True, text=True,
+                       cwd=os.path.dirname(pbrt_file))
+    if r.returncode != 0:
+        raise RuntimeError(f"dumpscene_ref failed ({r.returncode}): {r.stderr[-2000:]}")
+    return out_b2rs

@@ -17,46 +17,11 @@
 #include "device_scene.h"
 #include "kernels.h"
 #include "scene_host.h"
+#include "api_internal.h"
 
 using namespace b200pt;
 
-struct b200pt_ctx {
-    int device = 0;
-    int smCount = 0;
-    cudaStream_t stream = nullptr;
-    bool ownStream = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    std::string err;
-    // grow-only device staging for host-pointer calls
-    void *dIn = nullptr;
-    size_t dInCap = 0;
-    void *dOut = nullptr;
-    size_t dOutCap = 0;
-    unsigned long long *dCounters = nullptr;  // [0..2] trace counters, [7] ray-fetch counter
-    // scheduling knobs of the persistent kernel (B200PT_REFILL_MIN / B200PT_NODE_MIN override)
-    int refillMin = 4, nodeMin = 16;
-    bool simpleKernel = false;  // B200PT_TRAVERSAL=simple: the one-thread-per-ray parity kernel
-};
-
-struct b200pt_scene {
-    b200pt_ctx *ctx = nullptr;
-    HostScene host;
-    DeviceScene dev{};
-    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr, *dPairs = nullptr;
-    b200pt_scene_stats stats{};
-    b200pt_trace_stats trace{};
-};
-
-static std::string g_createErr;
-
-#define B2_CUDA(ctx, call)                                                                  \
-    do {                                                                                    \
-        cudaError_t e_ = (call);                                                            \
-        if (e_ != cudaSuccess) {                                                            \
-            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                \
-            return B200PT_ERR_CUDA;                                                         \
-        }                                                                                   \
-    } while (0)
+std::string g_createErr;
 
 extern "C" {
 

@@ -1,0 +1,238 @@
+// render_api.cpp - the render entry points of include/b200pt.h: table upload, the wavefront pass
+// loop that strings the kernels together (the role of WavefrontPathIntegrator::Render,
+// wavefront/integrator.cpp:290-493), film read-out.  Host code only; no CPU rendering path exists.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "api_internal.h"
+#include "kernels.h"
+#include "render_host.h"
+#include "render_kernels.h"
+
+using namespace b200pt;
+
+struct b200pt_render {
+    b200pt_scene *scene = nullptr;
+    RenderHost host;
+    RenderSceneDev dev{};
+    void *dSpectra = nullptr, *dMaterials = nullptr, *dLights = nullptr, *dMeshes = nullptr;
+    double *dFilm = nullptr;
+    float *dImage = nullptr;
+    void *dPaths = nullptr;
+    PathBuffers pb{};
+    long long pathCap = 0;
+    unsigned long long *dCounters = nullptr;  // [0] closest rays, [1] shadow rays
+    int *dRayCounter = nullptr;               // work counter of the persistent traversal kernel
+    int nPixels = 0;
+    long long maxPathsPerPass = 4ll << 20;    // B200PT_PASS_PATHS overrides
+    b200pt_render_stats stats{};
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+};
+
+namespace {
+template <class T>
+int Upload(b200pt_ctx *ctx, const std::vector<T> &v, void **d) {
+    size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+    B2_CUDA(ctx, cudaMalloc(d, bytes));
+    if (!v.empty()) B2_CUDA(ctx, cudaMemcpyAsync(*d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    return B200PT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int b200pt_render_destroy(b200pt_render *r) {
+    if (!r) return B200PT_OK;
+    if (r->scene && r->scene->ctx) {
+        cudaSetDevice(r->scene->ctx->device);
+        cudaStreamSynchronize(r->scene->ctx->stream);
+    }
+    cudaFree(r->dSpectra);
+    cudaFree(r->dMaterials);
+    cudaFree(r->dLights);
+    cudaFree(r->dMeshes);
+    cudaFree(r->dFilm);
+    cudaFree(r->dImage);
+    cudaFree(r->dPaths);
+    cudaFree(r->dCounters);
+    if (r->ev0) cudaEventDestroy(r->ev0);
+    if (r->ev1) cudaEventDestroy(r->ev1);
+    delete r;
+    return B200PT_OK;
+}
+
+int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b200pt_render **out) {
+    if (!scene || !desc || !out) return B200PT_ERR_INVALID;
+    *out = nullptr;
+    b200pt_ctx *ctx = scene->ctx;
+    b200pt_render *r = new (std::nothrow) b200pt_render;
+    if (!r) return B200PT_ERR_NOMEM;
+    r->scene = scene;
+    int rc = BuildRenderTables(desc, scene->host, scene->host.nMeshes, r->host, ctx->err);
+    if (rc != B200PT_OK) {
+        delete r;
+        return rc;
+    }
+    auto fail = [&](int code) {
+        b200pt_render_destroy(r);
+        return code;
+    };
+    if (cudaSetDevice(ctx->device) != cudaSuccess) {
+        ctx->err = "cudaSetDevice failed";
+        return fail(B200PT_ERR_CUDA);
+    }
+    if ((rc = Upload(ctx, r->host.spectra, &r->dSpectra)) || (rc = Upload(ctx, r->host.materials, &r->dMaterials)) ||
+        (rc = Upload(ctx, r->host.lights, &r->dLights)) || (rc = Upload(ctx, r->host.meshes, &r->dMeshes)))
+        return fail(rc);
+    r->nPixels = r->host.width * r->host.height;
+    r->dev = r->host.rs;
+    r->dev.spectra = (const SpectrumTable *)r->dSpectra;
+    r->dev.materials = (const MaterialDev *)r->dMaterials;
+    r->dev.lights = (const LightDev *)r->dLights;
+    r->dev.meshes = (const MeshAttrDev *)r->dMeshes;
+    r->dev.prims = scene->dev.prims;
+    if (const char *v = getenv("B200PT_PASS_PATHS")) r->maxPathsPerPass = std::max(1ll, atoll(v));
+    if (cudaMalloc((void **)&r->dFilm, sizeof(double) * 4 * r->nPixels) != cudaSuccess ||
+        cudaMalloc((void **)&r->dImage, sizeof(float) * 3 * r->nPixels) != cudaSuccess ||
+        cudaMalloc((void **)&r->dCounters, 4 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaEventCreate(&r->ev0) != cudaSuccess || cudaEventCreate(&r->ev1) != cudaSuccess ||
+        cudaMemsetAsync(r->dFilm, 0, sizeof(double) * 4 * r->nPixels, ctx->stream) != cudaSuccess ||
+        cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+        ctx->err = std::string("render setup: ") + cudaGetErrorString(cudaGetLastError());
+        return fail(B200PT_ERR_CUDA);
+    }
+    r->dRayCounter = (int *)(r->dCounters + 3);
+    *out = r;
+    return B200PT_OK;
+}
+
+int b200pt_film_clear(b200pt_render *r) {
+    if (!r) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2_CUDA(ctx, cudaMemsetAsync(r->dFilm, 0, sizeof(double) * 4 * r->nPixels, ctx->stream));
+    return B200PT_OK;
+}
+
+int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples, int32_t sample_stride) {
+    if (!r) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    if (first_sample < 0 || n_samples < 0 || sample_stride < 1) {
+        ctx->err = "render_run: bad sample range";
+        return B200PT_ERR_INVALID;
+    }
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int nPix = r->nPixels, width = r->host.width;
+    // samples of every pixel per pass, bounded by the path-buffer budget
+    int perPass = (int)std::max<long long>(1, std::min<long long>(n_samples, r->maxPathsPerPass / nPix));
+    long long need = (long long)perPass * nPix;
+    if (need > 0x7fffffffll) {
+        ctx->err = "render_run: film too large for one pass";
+        return B200PT_ERR_INVALID;
+    }
+    if (need > r->pathCap) {
+        B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        cudaFree(r->dPaths);
+        r->dPaths = nullptr;
+        r->pathCap = 0;
+        if (cudaMalloc(&r->dPaths, PathBufferBytes(need)) != cudaSuccess) {
+            (void)cudaGetLastError();
+            ctx->err = "render_run: out of device memory for the path buffers";
+            return B200PT_ERR_NOMEM;
+        }
+        CarvePathBuffers(r->dPaths, need, r->pb);
+        r->pathCap = need;
+    }
+    const DeviceScene &sc = r->scene->dev;
+    const int stackDepth = int(sc.maxDepth) + 1;
+    const int maxDepth = r->dev.integrator.maxDepth;
+    uint32_t launches = 0;
+    B2_CUDA(ctx, cudaMemsetAsync(r->dCounters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    B2_CUDA(ctx, cudaEventRecord(r->ev0, ctx->stream));
+    for (int done = 0; done < n_samples; done += perPass) {
+        int ns = std::min(perPass, n_samples - done);
+        int nActive = ns * nPix;
+        B2_CUDA(ctx, LaunchGenerate(r->dev, r->pb, nPix, width, nActive, first_sample + done * sample_stride,
+                                    sample_stride, r->dCounters, ctx->stream));
+        ++launches;
+        // vertex j: closest hit of the path ray, visibility of the shadow ray issued at vertex j-1, shade.
+        // Vertex maxDepth only collects emission and the last shadow ray (cpu/integrators.cpp:690-692).
+        for (int j = 0; j <= maxDepth; ++j) {
+            B2_CUDA(ctx, LaunchTraversePersist(sc, r->pb.rays, nActive, (b200pt_hit *)r->pb.hits, nullptr, false,
+                                               r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
+                                               ctx->nodeMin, ctx->stream, true));
+            ++launches;
+            if (j > 0) {
+                B2_CUDA(ctx, LaunchTraversePersist(sc, r->pb.shadowRays, nActive, nullptr, r->pb.occluded, true,
+                                                   r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
+                                                   ctx->nodeMin, ctx->stream, false));
+                ++launches;
+            }
+            B2_CUDA(ctx, LaunchShade(r->dev, r->pb, nPix, width, nActive, r->dCounters, ctx->stream));
+            ++launches;
+        }
+        B2_CUDA(ctx, LaunchFinish(r->dev, r->pb, nPix, nActive, ctx->stream));
+        B2_CUDA(ctx, LaunchFilmAdd(r->pb, nPix, ns, r->dFilm, ctx->stream));
+        launches += 2;
+    }
+    B2_CUDA(ctx, cudaEventRecord(r->ev1, ctx->stream));
+    r->timed = true;
+    r->stats.samples = (uint64_t)n_samples * nPix;
+    r->stats.kernel_launches = launches;
+    return B200PT_OK;
+}
+
+int b200pt_film_device_ptr(b200pt_render *r, void **ptr, uint64_t *n_doubles) {
+    if (!r || !ptr) return B200PT_ERR_INVALID;
+    *ptr = r->dFilm;
+    if (n_doubles) *n_doubles = 4ull * r->nPixels;
+    return B200PT_OK;
+}
+
+int b200pt_film_read(b200pt_render *r, double *rgb_weight) {
+    if (!r || !rgb_weight) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2_CUDA(ctx, cudaMemcpyAsync(rgb_weight, r->dFilm, sizeof(double) * 4 * r->nPixels, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200PT_OK;
+}
+
+int b200pt_film_image(b200pt_render *r, float *rgb) {
+    if (!r || !rgb) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2_CUDA(ctx, LaunchFilmImage(r->dev.film, r->dFilm, r->nPixels, r->dImage, ctx->stream));
+    B2_CUDA(ctx, cudaMemcpyAsync(rgb, r->dImage, sizeof(float) * 3 * r->nPixels, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200PT_OK;
+}
+
+int b200pt_render_get_stats(const b200pt_render *cr, b200pt_render_stats *out) {
+    if (!cr || !out) return B200PT_ERR_INVALID;
+    b200pt_render *r = const_cast<b200pt_render *>(cr);
+    b200pt_ctx *ctx = r->scene->ctx;
+    if (r->timed) {
+        B2_CUDA(ctx, cudaSetDevice(ctx->device));
+        B2_CUDA(ctx, cudaEventSynchronize(r->ev1));
+        float ms = 0;
+        B2_CUDA(ctx, cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+        unsigned long long c[2] = {0, 0};
+        B2_CUDA(ctx, cudaMemcpy(c, r->dCounters, sizeof(c), cudaMemcpyDeviceToHost));
+        r->stats.gpu_ms = ms;
+        r->stats.closest_rays = c[0];
+        r->stats.shadow_rays = c[1];
+    }
+    *out = r->stats;
+    return B200PT_OK;
+}
+
+}  // extern "C"

@@ -85,6 +85,7 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
         nTri += mesh.n_triangles;
     }
     out.nTriangles = nTri;
+    out.nMeshes = desc->n_meshes;
     if (desc->n_instances) {
         err = "instances are not supported by this build yet";
         return B200PT_ERR_INVALID;

@@ -32,6 +32,7 @@ struct HostScene {
     uint32_t maxDepth = 1;           // deepest path over all trees, in nodes
     float bounds[6] = {0, 0, 0, 0, 0, 0};
     uint64_t nTriangles = 0;
+    uint32_t nMeshes = 0;
     double buildSeconds = 0;
 };
 

@@ -52,7 +52,9 @@ enum : int { S_IDLE = 0, S_NODE = 1, S_LEAF = 2, S_DONE = 3 };
 constexpr int kSmemDepth = 24;
 constexpr int kLocalDepth = 72;
 
-template <bool ANY, bool COUNT>
+// INTERNAL: closest-hit records for the shading kernels {slot, t, b0, b1, b2, 0} instead of the
+// public b200pt_hit (the PrimSlot index saves the shader the (mesh, tri) -> vertices lookup).
+template <bool ANY, bool COUNT, bool INTERNAL>
 __global__ void __launch_bounds__(kBlock)
 TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200pt_hit *__restrict__ hits,
                       unsigned char *__restrict__ occluded, int *__restrict__ rayCounter,
@@ -68,7 +70,7 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
     int state = S_IDLE, rayIdx = -1;
     bool exhausted = false;
     RayCtx r;
-    float tMax = 0, bestB1 = 0, bestB2 = 0;
+    float tMax = 0, bestB0 = 0, bestB1 = 0, bestB2 = 0;
     int cur = 0, sp = 0, bestSlot = -1;
     unsigned long long cNodes = 0, cLeaves = 0, cPrims = 0;
 
@@ -177,6 +179,7 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                     }
                     tMax = t;
                     bestSlot = slot;
+                    if (INTERNAL) bestB0 = b0;
                     bestB1 = b1;
                     bestB2 = b2;
                 }
@@ -200,6 +203,10 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                     w0 = make_uint2(kMissTag, 0u);
                     w1 = make_uint2(0u, 0u);
                     w2 = make_uint2(0u, 0u);
+                } else if (INTERNAL) {
+                    w0 = make_uint2((unsigned)bestSlot, __float_as_uint(tMax));
+                    w1 = make_uint2(__float_as_uint(bestB0), __float_as_uint(bestB1));
+                    w2 = make_uint2(__float_as_uint(bestB2), 0u);
                 } else {
                     float4 b = __ldg(reinterpret_cast<const float4 *>(prims + 64ll * bestSlot + 32));
                     w0 = make_uint2(__float_as_uint(b.y), __float_as_uint(b.z));
@@ -225,7 +232,7 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
 cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long long n, b200pt_hit *hits,
                                   unsigned char *occluded, bool any, int *rayCounter,
                                   unsigned long long *counters, int smCount, int stackDepth,
-                                  int refillMin, int nodeMin, cudaStream_t stream) {
+                                  int refillMin, int nodeMin, cudaStream_t stream, bool internalHits) {
     if (n <= 0) return cudaSuccess;
     if (n > 0x7fffffffll) return cudaErrorInvalidValue;
     if (stackDepth > kSmemDepth + kLocalDepth) return cudaErrorInvalidValue;
@@ -245,8 +252,13 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
         return cudaGetLastError();
     };
     if (any)
-        return counters ? pick(TraversePersistKernel<true, true>) : pick(TraversePersistKernel<true, false>);
-    return counters ? pick(TraversePersistKernel<false, true>) : pick(TraversePersistKernel<false, false>);
+        return counters ? pick(TraversePersistKernel<true, true, false>)
+                        : pick(TraversePersistKernel<true, false, false>);
+    if (internalHits)
+        return counters ? pick(TraversePersistKernel<false, true, true>)
+                        : pick(TraversePersistKernel<false, false, true>);
+    return counters ? pick(TraversePersistKernel<false, true, false>)
+                    : pick(TraversePersistKernel<false, false, false>);
 }
 
 }  // namespace b200pt

@@ -58,3 +58,39 @@ def hit_mismatches(mine, ref):
     bad |= hit & ((mine["b2"] + z).view("u4") != (ref["uv"][:, 1] + z).view("u4"))
     bad |= hit & (((mine["b1"] + mine["b2"]).astype("f4") + z).view("u4") != (ref["uv"][:, 0] + z).view("u4"))
     return bad
+
+
+@pytest.fixture(scope="session")
+def rendercheck(P):
+    """TEST-ONLY host build of the render headers (tests/native/rendercheck.cpp): the same per-path
+    functions the CUDA kernels call, looped on the CPU.  Returns run(rscene, first, n, stride) -> film
+    accumulators [H, W, 4] float64."""
+    import ctypes as C
+    csrc = os.path.join(ROOT, "pbrt-v4_b200", "csrc")
+    out = os.path.join(ROOT, "tests", "native", "_build", "librendercheck.so")
+    src = [os.path.join(ROOT, "tests", "native", "rendercheck.cpp")] + \
+          [os.path.join(csrc, f) for f in ("scene_host.cpp", "bvh2_build.cpp", "render_host.cpp")]
+    deps = src + [os.path.join(csrc, h) for h in os.listdir(csrc) if h.endswith(".h")]
+    if not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-march=x86-64-v3", "-shared",
+                               "-fPIC", "-pthread", "-o", out] + src)
+    L = C.CDLL(out)
+
+    def run(rscene, first=0, n=None, stride=1, threads=8, use_host_bvh=False):
+        keep = []
+        sd = P.render.scene_desc(rscene.geometry, rscene.bvh if use_host_bvh else None, keep)
+        rd = rscene.desc(keep)
+        w, h = rscene.resolution
+        film = np.zeros((h, w, 4), np.float64)
+        msg = C.create_string_buffer(512)
+        rc = L.rendercheck_run(C.byref(sd), C.byref(rd), int(first), int(rscene.spp if n is None else n),
+                               int(stride), film.ctypes.data_as(C.POINTER(C.c_double)), msg, 512, threads)
+        assert rc == 0, msg.value.decode()
+        return film
+    return run
+
+
+def rrmse(img, ref):
+    """relative RMSE the way SURVEY.md 8c states the image gate: sqrt(mean((a-b)^2)) / mean(ref)."""
+    return float(np.sqrt(np.mean((np.asarray(img, np.float64) - ref) ** 2)) / np.mean(ref))

@@ -1,4 +1,5 @@
-"""Regenerates tests/golden/*.npz from the compiled reference (oracle/_ref/raycast_ref).
+"""Regenerates tests/golden/*.npz (ray batches, oracle/_ref/raycast_ref) and the whole-image
+fixtures *.b2rs + *_ref.npy (oracle/_ref/dumpscene_ref + pbrt_ref) from the compiled reference.
 Run in the build container (needs /root/reference -> `make -f oracle/ref.mk`):
     python tests/golden/make_golden.py
 Each fixture stores the ray batch and the reference's BVHAggregate::Intersect / IntersectP
@@ -43,10 +44,43 @@ def load(name):
             "shadow_occ": np.unpackbits(z["shadow_occ"])[:n]}
 
 
+# whole-image cases: name -> cornell_pbrt() arguments (config 1 of BASELINE.json, scaled down)
+RENDER_CASES = {
+    "cornell_r64_s16": dict(res=64, spp=16, maxdepth=5, lightsampler="power", seed=0),
+    "cornell_r48_s8_uniform": dict(res=48, spp=8, maxdepth=3, lightsampler="uniform", seed=3),
+}
+# scene tables only (no image): BASELINE.json configs[0] at full size, for bench.py and the
+# full-size GPU test, which render the reference image on the spot with oracle/_ref/pbrt_ref
+TABLE_CASES = {
+    "cornell_r512_s64": dict(res=512, spp=64, maxdepth=5, lightsampler="power", seed=0),
+}
+
+
+def make_render_goldens(P, refrun, out):
+    import tempfile
+    for name, kw in RENDER_CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            pbrt, pfm = os.path.join(tmp, name + ".pbrt"), os.path.join(tmp, name + ".pfm")
+            P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
+            img, secs = refrun.render(pbrt, pfm)
+            refrun.dump_scene(pbrt, os.path.join(out, name + ".b2rs"))
+            np.save(os.path.join(out, name + "_ref.npy"), img.astype(np.float32))
+            print(name, img.shape, "mean", img.mean(axis=(0, 1)), f"{secs:.2f}s")
+    for name, kw in TABLE_CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            pbrt = os.path.join(tmp, name + ".pbrt")
+            P.scenes.cornell_pbrt(pbrt, out=os.path.join(tmp, name + ".pfm"), **kw)
+            refrun.dump_scene(pbrt, os.path.join(out, name + ".b2rs"))
+            print(name, "tables only")
+
+
 if __name__ == "__main__":
     import pbrt_v4_b200 as P
     import refrun
     out = os.path.dirname(os.path.abspath(__file__))
+    make_render_goldens(P, refrun, out)
+    if "--render-only" in sys.argv:
+        sys.exit(0)
     for name, (sc, rays) in cases(P.scenes).items():
         rs = refrun.RefScene(sc)
         hits, _ = rs.closest(rays)

@@ -1,0 +1,134 @@
+"""Whole-image parity of the CUDA render path (through the C-ABI: b200pt_render_create / render_run /
+film_read / film_image) against the reference CPU PathIntegrator's images (committed fixtures) and
+against the CPU loop over the same headers.  Same tolerance as tests/test_render_cpu.py; the GPU's
+sinf/cosf/atan2f differ from glibc's in the last ulp, so GPU == CPU-check is a tolerance too."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, rrmse
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(ROOT, "tests", "golden")
+TOL_RRMSE = 1e-3
+TOL_MEAN = 1e-4
+
+
+@pytest.fixture(scope="module")
+def cornell(P):
+    return P.RenderScene.load(os.path.join(GOLD, "cornell_r64_s16.b2rs"))
+
+
+@pytest.mark.parametrize("name", ["cornell_r64_s16", "cornell_r48_s8_uniform"])
+@pytest.mark.parametrize("host_bvh", [False, True])
+def test_golden_image(P, name, host_bvh):
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    r = P.B200Renderer(rsc, use_host_bvh=host_bvh)
+    try:
+        r.render()
+        img, film = r.image(), r.film()
+        st = r.stats()
+    finally:
+        r.close()
+    assert np.all(film[..., 3] == rsc.spp)
+    assert rrmse(img, ref) <= TOL_RRMSE
+    assert abs(img.mean() - ref.mean()) <= TOL_MEAN * ref.mean()
+    np.testing.assert_allclose(img, P.render.film_to_image(film, rsc.d["film_matrix"]), rtol=1e-6, atol=1e-7)
+    assert st["samples"] == rsc.spp * img.shape[0] * img.shape[1]
+    assert st["closest_rays"] >= st["samples"] and st["shadow_rays"] > 0 and st["kernel_launches"] > 0
+
+
+def test_matches_cpu_check(P, cornell, rendercheck):
+    r = P.B200Renderer(cornell)
+    try:
+        r.render()
+        film = r.film()
+    finally:
+        r.close()
+    cpu = rendercheck(cornell)
+    a, b = (P.render.film_to_image(f, cornell.d["film_matrix"]) for f in (film, cpu))
+    assert rrmse(a, b) <= 1e-4
+
+
+def test_passes_and_striping(P, cornell, monkeypatch):
+    """Small pass budget (many passes) and 2-way sample striping give the single-pass film."""
+    r = P.B200Renderer(cornell)
+    try:
+        r.render()
+        whole = r.film()
+        r.clear()
+        r.render(0, cornell.spp // 2, 2)
+        r.render(1, cornell.spp // 2, 2)
+        striped = r.film()
+    finally:
+        r.close()
+    np.testing.assert_allclose(striped, whole, rtol=1e-12, atol=0)
+    monkeypatch.setenv("B200PT_PASS_PATHS", str(3 * 64 * 64))
+    r = P.B200Renderer(cornell)
+    try:
+        r.render()
+        small = r.film()
+    finally:
+        r.close()
+    assert np.array_equal(small, whole)
+
+
+def test_deterministic(P, cornell):
+    r = P.B200Renderer(cornell)
+    try:
+        r.render()
+        a = r.film()
+        r.clear()
+        r.render()
+        b = r.film()
+    finally:
+        r.close()
+    assert np.array_equal(a, b)
+
+
+def test_bad_arguments(P, cornell):
+    import ctypes as C
+    r = P.B200Renderer(cornell)
+    try:
+        with pytest.raises(P.capi.B200PTError):
+            r.render(0, 4, 0)
+        with pytest.raises(P.capi.B200PTError):
+            r.render(-1, 4, 1)
+    finally:
+        r.close()
+    keep = []
+    agg = P.B200Aggregate(cornell.geometry)
+    try:
+        d = cornell.desc(keep)
+        d.n_meshes += 1
+        out = C.c_void_p()
+        assert P.capi.lib().b200pt_render_create(agg._scene, C.byref(d), C.byref(out)) != 0
+    finally:
+        agg.close()
+
+
+def test_full_size_config1(P, refrun, tmp_path):
+    """BASELINE.json configs[0] at full size (512x512, 64 spp, maxdepth 5) against the reference
+    rendered on this box's host cores by oracle/_ref/pbrt_ref (the compiled reference travels with the
+    repo; /root/reference is not needed)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(GOLD, "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    TABLE_CASES = mg.TABLE_CASES
+    if not refrun.render_available():
+        pytest.skip("oracle/_ref/pbrt_ref not present")
+    pbrt, pfm = str(tmp_path / "c.pbrt"), str(tmp_path / "c.pfm")
+    P.scenes.cornell_pbrt(pbrt, out=pfm, **TABLE_CASES["cornell_r512_s64"])
+    ref, _ = refrun.render(pbrt, pfm)
+    rsc = P.RenderScene.load(os.path.join(GOLD, "cornell_r512_s64.b2rs"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img = r.image()
+    finally:
+        r.close()
+    assert rrmse(img, ref) <= TOL_RRMSE
+    assert abs(img.mean() - ref.mean()) <= TOL_MEAN * ref.mean()
