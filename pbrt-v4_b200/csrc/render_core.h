@@ -41,19 +41,23 @@ B2_HD void ZSobolStart(ZSobol &s, const SamplerDev &sd, int px, int py, int inde
     s.mortonIndex = (EncodeMorton2(px, py) << sd.log2Spp) | (uint64_t)index;
 }
 
-// the 24 permutations of 4 digits in the reference's order (samplers.h:300-326); packed 2 bits each
+// the 24 permutations of 4 digits in the reference's order (samplers.h:300-326), one byte each
+// ({a,b,c,d} -> a | b<<2 | c<<4 | d<<6), packed into three 64-bit words so the lookup is shifts on
+// registers (a byte table indexed per thread would live in local memory on the device).
 B2_HD int ZSobolPermute(int p, int digit) {
-    const uint8_t perms[24] = {
-        // {a,b,c,d} -> a | b<<2 | c<<4 | d<<6
-        0 | 1 << 2 | 2 << 4 | 3 << 6, 0 | 1 << 2 | 3 << 4 | 2 << 6, 0 | 2 << 2 | 1 << 4 | 3 << 6,
-        0 | 2 << 2 | 3 << 4 | 1 << 6, 0 | 3 << 2 | 2 << 4 | 1 << 6, 0 | 3 << 2 | 1 << 4 | 2 << 6,
-        1 | 0 << 2 | 2 << 4 | 3 << 6, 1 | 0 << 2 | 3 << 4 | 2 << 6, 1 | 2 << 2 | 0 << 4 | 3 << 6,
-        1 | 2 << 2 | 3 << 4 | 0 << 6, 1 | 3 << 2 | 2 << 4 | 0 << 6, 1 | 3 << 2 | 0 << 4 | 2 << 6,
-        2 | 1 << 2 | 0 << 4 | 3 << 6, 2 | 1 << 2 | 3 << 4 | 0 << 6, 2 | 0 << 2 | 1 << 4 | 3 << 6,
-        2 | 0 << 2 | 3 << 4 | 1 << 6, 2 | 3 << 2 | 0 << 4 | 1 << 6, 2 | 3 << 2 | 1 << 4 | 0 << 6,
-        3 | 1 << 2 | 2 << 4 | 0 << 6, 3 | 1 << 2 | 0 << 4 | 2 << 6, 3 | 2 << 2 | 1 << 4 | 0 << 6,
-        3 | 2 << 2 | 0 << 4 | 1 << 6, 3 | 0 << 2 | 2 << 4 | 1 << 6, 3 | 0 << 2 | 1 << 4 | 2 << 6};
-    return (perms[p] >> (2 * digit)) & 3;
+#define B2_PERM(a, b, c, d) uint64_t((a) | (b) << 2 | (c) << 4 | (d) << 6)
+#define B2_PERM8(p0, p1, p2, p3, p4, p5, p6, p7) \
+    ((p0) | (p1) << 8 | (p2) << 16 | (p3) << 24 | (p4) << 32 | (p5) << 40 | (p6) << 48 | (p7) << 56)
+    const uint64_t w0 = B2_PERM8(B2_PERM(0, 1, 2, 3), B2_PERM(0, 1, 3, 2), B2_PERM(0, 2, 1, 3), B2_PERM(0, 2, 3, 1),
+                                 B2_PERM(0, 3, 2, 1), B2_PERM(0, 3, 1, 2), B2_PERM(1, 0, 2, 3), B2_PERM(1, 0, 3, 2));
+    const uint64_t w1 = B2_PERM8(B2_PERM(1, 2, 0, 3), B2_PERM(1, 2, 3, 0), B2_PERM(1, 3, 2, 0), B2_PERM(1, 3, 0, 2),
+                                 B2_PERM(2, 1, 0, 3), B2_PERM(2, 1, 3, 0), B2_PERM(2, 0, 1, 3), B2_PERM(2, 0, 3, 1));
+    const uint64_t w2 = B2_PERM8(B2_PERM(2, 3, 0, 1), B2_PERM(2, 3, 1, 0), B2_PERM(3, 1, 2, 0), B2_PERM(3, 1, 0, 2),
+                                 B2_PERM(3, 2, 1, 0), B2_PERM(3, 2, 0, 1), B2_PERM(3, 0, 2, 1), B2_PERM(3, 0, 1, 2));
+#undef B2_PERM8
+#undef B2_PERM
+    uint64_t w = p < 8 ? w0 : (p < 16 ? w1 : w2);
+    return (int)(w >> (8 * (p & 7) + 2 * digit)) & 3;
 }
 
 B2_HD uint64_t ZSobolSampleIndex(const ZSobol &s) {  // samplers.h:298-353
@@ -75,15 +79,27 @@ B2_HD uint64_t ZSobolSampleIndex(const ZSobol &s) {  // samplers.h:298-353
     return sampleIndex;
 }
 
-// Sobol' generator matrices of dimensions 0 and 1 (the only ones ZSobol uses): dimension 0 is the
-// van der Corput radical inverse, dimension 1 has column j = binomial(j, i) mod 2 - the same values
-// as SobolMatrices32[0..103] (util/sobolmatrices.cpp:40-58; checked in tests/test_render_core.py).
+// Sobol' generator matrices of dimensions 0 and 1 (the only ones ZSobol uses; SobolMatrices32[0..103],
+// util/sobolmatrices.cpp:40-58).  Dimension 0 is the identity (bit j -> 0x80000000 >> j: a bit
+// reversal).  Dimension 1 is Pascal's triangle mod 2: column j has bit (31 - i) set iff
+// binomial(j, i) is odd, i.e. iff i is a bit-subset of j (Lucas); for j >= 32 only j & 31 matters.
+// SobolColumn states that definition (tests compare it with the reference's table); the product with
+// an index is then a superset-XOR over the index bits, done in five butterfly steps (SobolDim1).
 B2_HD uint32_t SobolColumn(int dim, int j) {
     if (dim == 0) return j < 32 ? (0x80000000u >> j) : 0u;
     uint32_t v = 0;
     for (int i = 0; i < 32; ++i)
         if ((i & ~j) == 0) v |= 0x80000000u >> i;
     return v;
+}
+B2_HD uint32_t SobolDim1(uint64_t a) {
+    uint32_t x = (uint32_t)a ^ (uint32_t)(a >> 32);  // columns repeat with period 32
+    x ^= (x >> 1) & 0x55555555u;                     // out[i] = XOR of in[j] over all j that contain i
+    x ^= (x >> 2) & 0x33333333u;
+    x ^= (x >> 4) & 0x0f0f0f0fu;
+    x ^= (x >> 8) & 0x00ff00ffu;
+    x ^= (x >> 16) & 0x0000ffffu;
+    return ReverseBits32(x);
 }
 B2_HD uint32_t FastOwen(uint32_t v, uint32_t seed) {  // util/lowdiscrepancy.h:221-237
     v = ReverseBits32(v);
@@ -103,13 +119,7 @@ B2_HD uint32_t OwenScramble(uint32_t v, uint32_t seed) {  // util/lowdiscrepancy
     return v;
 }
 B2_HD float SobolSampleZ(uint64_t a, int dim, uint32_t randomize, uint32_t hash) {  // util/lowdiscrepancy.h:168-180
-    uint32_t v = 0;
-    if (dim == 0) {
-        v = ReverseBits32((uint32_t)a);  // sum of 0x80000000 >> j over set bits j < 32
-    } else {
-        for (int j = 0; a != 0; a >>= 1, ++j)
-            if (a & 1) v ^= SobolColumn(1, j);
-    }
+    uint32_t v = dim == 0 ? ReverseBits32((uint32_t)a) : SobolDim1(a);
     if (randomize == 1) v ^= hash;
     else if (randomize == 2) v = FastOwen(v, hash);
     else if (randomize == 3) v = OwenScramble(v, hash);
@@ -141,7 +151,8 @@ B2_HD void SampleWavelengths(float u, float lambda[kNLambda]) {
 }
 B2_HD float SpectrumAt(const SpectrumTable &t, float lambda) {
     if (t.interp == 0) {  // DenselySampledSpectrum::Sample (util/spectrum.h:420-430)
-        int offset = (int)lroundf(lambda) - (int)kLambdaMin;
+        // std::lround(lambda); for 0 < lambda < 2^22, lambda + 0.5f is exact or a tie that floors alike
+        int offset = (int)floorf(lambda + 0.5f) - (int)kLambdaMin;
         return (offset < 0 || offset >= kSpecTable) ? 0.f : t.values[offset];
     }
     float x = lambda - kLambdaMin;

@@ -121,3 +121,11 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     for (auto &th : pool) th.join();
     return 0;
 }
+
+// ---- small probes for tests/test_render_core.py
+extern "C" uint32_t rendercheck_sobol_column(int dim, int j) { return b200pt::SobolColumn(dim, j); }
+extern "C" uint32_t rendercheck_sobol_dim1(uint64_t a) { return b200pt::SobolDim1(a); }
+extern "C" int rendercheck_permute(int p, int digit) { return b200pt::ZSobolPermute(p, digit); }
+extern "C" float rendercheck_spectrum_at(const b200pt_spectrum *s, float lambda) {
+    return b200pt::SpectrumAt(*reinterpret_cast<const b200pt::SpectrumTable *>(s), lambda);
+}
