@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--rays", type=int, default=1 << 24, help="primary rays per step (as many shadow rays)")
     ap.add_argument("--cpu-sample", type=int, default=1 << 21, help="rays of each kind in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-render", action="store_true", help="skip the config-1 end-to-end render section")
+    ap.add_argument("--render-cpu-spp", type=int, default=16, help="spp of the bounded pbrt_ref sample")
     return ap.parse_args()
 
 
@@ -118,6 +120,91 @@ def make_batches(P, agg, n, seed):
     return prim, shad
 
 
+RENDER_CASE = "cornell_r512_s64"  # BASELINE.json configs[0]; tables in tests/golden (make_golden.py TABLE_CASES)
+RENDER_KW = dict(res=512, spp=64, maxdepth=5, lightsampler="power", seed=0)
+
+
+class _DevArray:
+    """A device pointer as __cuda_array_interface__, so torch can alias the library's film buffer."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def render_cpu_reference(args, P):
+    """pbrt_ref (the reference's own main, CPU PathIntegrator) on a bounded sample of config 1:
+    the same scene and resolution at --render-cpu-spp samples per pixel, all host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refrun
+    if not refrun.render_available():
+        return {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    kw = dict(RENDER_KW, spp=args.render_cpu_spp)
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt, pfm = os.path.join(tmp, "c.pbrt"), os.path.join(tmp, "c.pfm")
+        P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
+        _, secs = refrun.render(pbrt, pfm)
+    n = kw["res"] * kw["res"] * kw["spp"]
+    return {"value": n / secs * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
+            "seconds": secs,
+            "sample": f"Cornell {kw['res']}x{kw['res']} at {kw['spp']} spp (config 1 is 64 spp), wall clock of the "
+                      f"whole pbrt_ref process incl. parse + BVH build (36 triangles)"}
+
+
+def render_section(args, P, torch, dist, rank, world, local, stream, barrier):
+    """Config 1 end to end: Msamples/s of the whole frame (sample stripes per rank, NCCL film reduce,
+    film read-back on rank 0)."""
+    rsc = P.RenderScene.load(os.path.join(ROOT, "tests", "golden", RENDER_CASE + ".b2rs"))
+    spp = rsc.spp
+    r = P.B200Renderer(rsc, device=local, stream=stream.cuda_stream)
+    ptr, nd = r.film_device_ptr()
+    film_t = torch.as_tensor(_DevArray(ptr, nd, "<f8"), device="cuda")
+
+    def frame(read):
+        r.clear()
+        r.render(*P.parallel.sample_stripe(spp, rank, world))
+        P.parallel.reduce_film(film_t, dist)
+        return r.image() if (read and rank == 0) else None
+
+    for _ in range(args.warmup):
+        frame(False)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        frame(False)
+    e1.record(stream)
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    st = r.stats()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        img = frame(True)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_s = (float(x) for x in t.cpu())
+    w, h = rsc.resolution
+    n = w * h * spp * args.steps
+    out = None
+    if rank == 0:
+        out = {"metric": "render_msamples_per_s", "unit": "Msamples/s", "value": n / (dev_ms * 1e-3) * 1e-6,
+               "ms_per_frame": dev_ms / args.steps, "scaling": "strong",
+               "workload": f"config1: Cornell box {w}x{h}, {spp} spp, path maxdepth 5, zsobol, power light sampler; "
+                           f"sample stripes over {world} rank(s), film reduced by NCCL",
+               "e2e": {"value": n / e2e_s * 1e-6, "unit": "Msamples/s", "h2d_bytes_per_step": 0,
+                       "d2h_bytes_per_step": w * h * 12,
+                       "note": "scene tables resident; per frame: clear + render + reduce + final image to host"},
+               "rays_per_frame": (st["closest_rays"] + st["shadow_rays"]) * world,
+               "launches_per_frame": st["kernel_launches"], "image_mean": float(img.mean())}
+        if not args.no_cpu_baseline:
+            out["cpu_baseline"] = render_cpu_reference(args, P)
+    r.close()
+    return out
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU BVHAggregate on all host cores, bounded sample per step."""
     if rank != 0:
@@ -152,6 +239,10 @@ def run_reference(args, rank, world):
                                        f"{reps} passes, BVH build excluded ({ic['build_s']:.2f} s)"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    if not args.no_render:
+        rc = render_cpu_reference(args, P)
+        line["render"] = {"metric": "render_msamples_per_s", "unit": "Msamples/s", "value": rc["value"],
+                          "cpu_baseline": rc}
     print(json.dumps(line), flush=True)
 
 
@@ -249,6 +340,10 @@ def main():
     if rank == 0:
         assert np.array_equal(h_hits.numpy(), d_hits.cpu().numpy()) and np.array_equal(h_occ.numpy(), d_occ.cpu().numpy())
 
+    render = None
+    if not args.no_render:
+        render = render_section(args, P, torch, dist, rank, world, local, stream, barrier)
+
     # ---- max over ranks
     t = torch.tensor([total_ms, e2e_s, ms_closest, ms_any], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -276,6 +371,7 @@ def main():
             "e2e": {"value": rays_total / e2e_s * 1e-6, "unit": UNIT,
                     "h2d_bytes_per_step": 2 * n * 28, "d2h_bytes_per_step": n * 24 + n},
             "gpu_launches": 2 * args.steps,
+            "render": render,
             "clocks": clk,
             "scene": {"bvh2_nodes": st["n_bvh2_nodes"], "wide_nodes": st["n_wide_nodes"],
                       "device_bytes": st["device_bytes"], "build_s": st["build_seconds"]},

@@ -7,7 +7,7 @@ include/b200pt.h).  This package is the thin Python host side: a ctypes binding
 There is no CPU path: everything that computes raises if the library or a GPU
 is missing.
 """
-from . import capi, scenes, render  # noqa: F401
+from . import capi, scenes, render, parallel  # noqa: F401
 from .aggregate import B200Aggregate  # noqa: F401
 from .render import B200Renderer, RenderScene  # noqa: F401
 from ._build import build  # noqa: F401
