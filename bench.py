@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=1 << 21, help="rays of each kind in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true", help="skip the config-1 end-to-end render section")
-    ap.add_argument("--render-cpu-spp", type=int, default=16, help="spp of the bounded pbrt_ref sample")
+    ap.add_argument("--render-cpu-spp", type=int, default=64, help="spp of the bounded pbrt_ref sample")
     return ap.parse_args()
 
 
