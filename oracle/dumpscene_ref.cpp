@@ -25,6 +25,7 @@
 #include <pbrt/pbrt.h>
 #include <pbrt/cameras.h>
 #include <pbrt/cpu/aggregates.h>
+#include <pbrt/cpu/integrators.h>
 #include <pbrt/cpu/primitive.h>
 #include <pbrt/film.h>
 #include <pbrt/filters.h>
@@ -150,6 +151,72 @@ int main(int argc, char **argv) {
     Camera camera = scene.GetCamera();
     Film film = camera.GetFilm();
     Sampler sampler = scene.GetSampler();
+
+    // ---- debug mode: `dumpscene_ref scene.pbrt --path x y sampleIndex` prints, for one pixel sample, the
+    // radiance the reference's PathIntegrator::Li returns when maxDepth is cut at 0, 1, 2, ... (the
+    // increments are the per-vertex contributions), to localise a divergence of our kernels.
+    if (std::string(argv[2]) == "--path") {
+        if (argc < 6) die("usage: dumpscene_ref scene.pbrt --path x y sampleIndex");
+        int px = atoi(argv[3]), py = atoi(argv[4]), si = atoi(argv[5]);
+        std::unique_ptr<Integrator> integ(scene.CreateIntegrator(camera, sampler, accel, lights));
+        PathIntegrator *pi = dynamic_cast<PathIntegrator *>(integ.get());
+        if (!pi) die("--path needs the path integrator");
+        int fullDepth = pi->maxDepth;
+        ScratchBuffer scratch(65536);
+        for (int d = 0; d <= fullDepth; ++d) {
+            pi->maxDepth = d;
+            Sampler s = sampler.Clone(Allocator());
+            s.StartPixelSample(Point2i(px, py), si, 0);
+            Float lu = s.Get1D();
+            SampledWavelengths lambda = film.SampleWavelengths(lu);
+            CameraSample cs = GetCameraSample(s, Point2i(px, py), film.GetFilter());
+            pstd::optional<CameraRayDifferential> cr = camera.GenerateRayDifferential(cs, lambda);
+            SampledSpectrum L = pi->Li(cr->ray, lambda, s, scratch, nullptr);
+            printf("maxdepth %d  lambda0 %.9g  o %.9g %.9g %.9g  d %.9g %.9g %.9g  L0 %.9g L1 %.9g L15 %.9g L30 %.9g  dim %d\n", d,
+                   lambda[0], cr->ray.o.x, cr->ray.o.y, cr->ray.o.z, cr->ray.d.x, cr->ray.d.y, cr->ray.d.z, L[0], L[1],
+                   L[15], L[30], s.Is<ZSobolSampler>() ? s.Cast<ZSobolSampler>()->dimension : -1);
+            scratch.Reset();
+        }
+        // the same path once more, vertex by vertex, through the reference's own Intersect / GetBSDF /
+        // Sample_f (a driver loop over the reference API, printing the state Li keeps to itself)
+        {
+            Sampler s = sampler.Clone(Allocator());
+            s.StartPixelSample(Point2i(px, py), si, 0);
+            Float lu = s.Get1D();
+            SampledWavelengths lambda = film.SampleWavelengths(lu);
+            CameraSample cs = GetCameraSample(s, Point2i(px, py), film.GetFilter());
+            RayDifferential ray = camera.GenerateRayDifferential(cs, lambda)->ray;
+            SampledSpectrum beta(1.f);
+            Float etaScale = 1;
+            for (int depth = 0; depth < fullDepth; ++depth) {
+                pstd::optional<ShapeIntersection> isr = accel.Intersect(ray, Infinity);
+                if (!isr) break;
+                SurfaceInteraction &isect = isr->intr;
+                BSDF bsdf = isect.GetBSDF(ray, lambda, camera, scratch, s);
+                if (!bsdf) break;
+                int dim0 = s.Cast<ZSobolSampler>()->dimension;
+                if (IsNonSpecular(bsdf.Flags())) { s.Get1D(); s.Get2D(); }
+                Vector3f wo = -ray.d;
+                Float u = s.Get1D();
+                pstd::optional<BSDFSample> bs = bsdf.Sample_f(wo, u, s.Get2D());
+                if (!bs) break;
+                beta *= bs->f * AbsDot(bs->wi, isect.shading.n) / bs->pdf;
+                if (bs->IsTransmission()) etaScale *= Sqr(bs->eta);
+                SampledSpectrum rrBeta = beta * etaScale;
+                printf("   ref vertex %d: t %.9g dim %d f0 %.9g absdot %.9g pdf %.9g eta %.9g -> beta0 %.9g etaScale %.9g rr %.9g wi %.9g %.9g %.9g\n",
+                       depth, isr->tHit, dim0, bs->f[0], AbsDot(bs->wi, isect.shading.n), bs->pdf, bs->eta, beta[0], etaScale,
+                       rrBeta.MaxComponentValue(), bs->wi.x, bs->wi.y, bs->wi.z);
+                ray = isect.SpawnRay(ray, bsdf, bs->wi, bs->flags, bs->eta);
+                if (rrBeta.MaxComponentValue() < 1 && depth + 1 > 1) {
+                    Float q = std::max<Float>(0, 1 - rrBeta.MaxComponentValue());
+                    if (s.Get1D() < q) break;
+                    beta /= 1 - q;
+                }
+            }
+        }
+        fflush(stdout);
+        _Exit(0);
+    }
 
     Writer w(argv[2]);
     SpectraPool pool;
@@ -282,18 +349,60 @@ int main(int argc, char **argv) {
     // ---- materials
     std::vector<int32_t> matI;
     std::vector<float> matF;
+    auto constSpec = [&](SpectrumTexture t) -> int {
+        if (!t) return -1;
+        const SpectrumConstantTexture *ct = t.CastOrNullptr<SpectrumConstantTexture>();
+        if (!ct) die("only constant spectrum textures are dumped so far");
+        return pool.add(ct->value, 1);
+    };
+    auto constFloat = [&](FloatTexture t) -> float {
+        const FloatConstantTexture *ct = t.CastOrNullptr<FloatConstantTexture>();
+        if (!ct) die("only constant float textures are dumped so far");
+        return ct->value;
+    };
+    // materials_i: {type, spectrum[4]}; materials_f: params[8] (layout: include/b200pt.h b200pt_material)
     for (pbrt::Material mtl : materialList) {
         int32_t rec[5] = {-1, -1, -1, -1, -1};
         float prm[8] = {0};
         if (!mtl) {
             rec[0] = -1;
         } else if (const DiffuseMaterial *dm = mtl.CastOrNullptr<DiffuseMaterial>()) {
-            const SpectrumConstantTexture *ct = dm->reflectance.CastOrNullptr<SpectrumConstantTexture>();
-            if (!ct) die("only constant reflectance textures are dumped so far");
+            if (dm->displacement || dm->normalMap) die("displacement / normal maps are not dumped");
             rec[0] = 0;
-            rec[1] = pool.add(ct->value, 1);
+            rec[1] = constSpec(dm->reflectance);
+        } else if (const ConductorMaterial *cm = mtl.CastOrNullptr<ConductorMaterial>()) {
+            if (cm->displacement || cm->normalMap) die("displacement / normal maps are not dumped");
+            rec[0] = 1;
+            rec[1] = constSpec(cm->eta);
+            rec[2] = constSpec(cm->k);
+            rec[3] = constSpec(cm->reflectance);
+            prm[0] = constFloat(cm->uRoughness);
+            prm[1] = constFloat(cm->vRoughness);
+            prm[2] = cm->remapRoughness ? 1.f : 0.f;
+        } else if (const DielectricMaterial *em = mtl.CastOrNullptr<DielectricMaterial>()) {
+            if (em->displacement || em->normalMap) die("displacement / normal maps are not dumped");
+            rec[0] = 2;
+            rec[1] = pool.add(em->eta, 1);
+            prm[0] = constFloat(em->uRoughness);
+            prm[1] = constFloat(em->vRoughness);
+            prm[2] = em->remapRoughness ? 1.f : 0.f;
+            prm[3] = em->eta.Is<ConstantSpectrum>() ? 1.f : 0.f;
+        } else if (const CoatedDiffuseMaterial *cd = mtl.CastOrNullptr<CoatedDiffuseMaterial>()) {
+            if (cd->displacement || cd->normalMap) die("displacement / normal maps are not dumped");
+            rec[0] = 3;
+            rec[1] = constSpec(cd->reflectance);
+            rec[2] = constSpec(cd->albedo);
+            rec[3] = pool.add(cd->eta, 1);
+            prm[0] = constFloat(cd->uRoughness);
+            prm[1] = constFloat(cd->vRoughness);
+            prm[2] = cd->remapRoughness ? 1.f : 0.f;
+            prm[3] = cd->eta.Is<ConstantSpectrum>() ? 1.f : 0.f;
+            prm[4] = constFloat(cd->thickness);
+            prm[5] = constFloat(cd->g);
+            prm[6] = float(cd->maxDepth);
+            prm[7] = float(cd->nSamples);
         } else
-            die("only diffuse materials are dumped so far");
+            die("only diffuse, conductor, dielectric and coateddiffuse materials are dumped so far");
         matI.insert(matI.end(), rec, rec + 5);
         matF.insert(matF.end(), prm, prm + 8);
     }

@@ -14,6 +14,7 @@ cudaError_t LaunchTraverseBVH2(const DeviceScene &sc, const float *rays, long lo
 cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long long n, b200pt_hit *hits,
                                   unsigned char *occluded, bool any, int *rayCounter,
                                   unsigned long long *counters, int smCount, int stackDepth,
-                                  int refillMin, int nodeMin, cudaStream_t stream, bool internalHits = false);
+                                  int refillMin, int nodeMin, cudaStream_t stream, bool internalHits = false,
+                                  const int *nDev = nullptr);
 
 }  // namespace b200pt

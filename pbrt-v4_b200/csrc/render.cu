@@ -1,12 +1,14 @@
-// render.cu - the wavefront kernels around the traversal kernel: camera-ray generation, the
-// per-vertex shading step (emission, BSDF, light sampling with its shadow ray, Russian roulette),
-// sample finish (sensor RGB) and film accumulation.  All path logic is in render_core.h (shared with
-// the CPU check in tests/native/rendercheck.cpp); these kernels only move a path between its
-// structure-of-arrays slot and registers.
+// render.cu - the wavefront kernels around the traversal kernel: camera-ray generation, hit
+// classification into material-sorted queues, the per-vertex shading step (emission, BSDF, light
+// sampling with its shadow ray, Russian roulette), shadow-ray resolution, sample finish (sensor RGB)
+// and film accumulation.  All path logic is in render_core.h (shared with the CPU check in
+// tests/native/rendercheck.cpp); these kernels move a path between its structure-of-arrays slot and
+// registers and feed the queues.
 //
-// Stage order per pass (api.cpp RenderRun), mirroring WavefrontPathIntegrator::Render
-// (wavefront/integrator.cpp:290-493): generate -> for each depth { closest-hit ; any-hit of the shadow
-// rays of the previous vertex ; shade } -> finish -> film.
+// Stage order per pass (render_api.cpp), mirroring WavefrontPathIntegrator::Render
+// (wavefront/integrator.cpp:290-493):
+//   generate -> for each depth { closest-hit ; classify ; shade<material> ... ; any-hit ; resolve }
+//            -> finish -> film.
 #include <cuda_runtime.h>
 
 #include "render_core.h"
@@ -16,38 +18,56 @@ namespace b200pt {
 
 constexpr int kShadeBlock = 128;
 
-size_t PathBufferBytes(long long n) {
-    auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
+static size_t Al(size_t b) { return (b + 255) & ~size_t(255); }
+
+size_t PassBufferBytes(long long n, int depthSlots) {
     size_t t = 0;
-    t += al(sizeof(float) * 3 * kNLambda * n);
-    t += al(sizeof(float) * kPathScalars * n);
-    t += al(sizeof(int) * kPathInts * n);
-    t += 2 * al(sizeof(float) * 7 * n);
-    t += al(sizeof(uint32_t) * 6 * n);
-    t += al(size_t(n));
-    t += al(sizeof(float) * 4 * n);
+    t += 2 * Al(sizeof(float) * kNLambda * n);         // beta, L
+    t += Al(sizeof(float) * kPathScalars * n);
+    t += Al(sizeof(int) * kPathInts * n);
+    t += Al(sizeof(float) * 4 * n);                    // rgbw
+    t += 2 * Al(sizeof(float) * 7 * n) + 2 * Al(sizeof(int) * n);  // rays, rayPath
+    t += Al(sizeof(uint32_t) * 6 * n);                 // hits
+    t += kMatQueues * Al(sizeof(int) * n);
+    t += Al(sizeof(float) * 7 * n) + Al(sizeof(int) * n) + Al(sizeof(float) * kNLambda * n) + Al(size_t(n));
+    t += Al(sizeof(int) * kCountStride * depthSlots);
     return t;
 }
 
-void CarvePathBuffers(void *base, long long n, PathBuffers &pb) {
+void CarvePassBuffers(void *base, long long n, int depthSlots, PassBuffers &pb) {
     char *p = static_cast<char *>(base);
     auto take = [&](size_t b) {
         char *r = p;
-        p += (b + 255) & ~size_t(255);
+        p += Al(b);
         return r;
     };
     pb.n = (int)n;
-    pb.spec = (float *)take(sizeof(float) * 3 * kNLambda * n);
+    pb.beta = (float *)take(sizeof(float) * kNLambda * n);
+    pb.L = (float *)take(sizeof(float) * kNLambda * n);
     pb.scalars = (float *)take(sizeof(float) * kPathScalars * n);
     pb.ints = (int *)take(sizeof(int) * kPathInts * n);
-    pb.rays = (float *)take(sizeof(float) * 7 * n);
-    pb.shadowRays = (float *)take(sizeof(float) * 7 * n);
-    pb.hits = (uint32_t *)take(sizeof(uint32_t) * 6 * n);
-    pb.occluded = (unsigned char *)take(size_t(n));
     pb.rgbw = (float *)take(sizeof(float) * 4 * n);
+    for (int i = 0; i < 2; ++i) pb.rays[i] = (float *)take(sizeof(float) * 7 * n);
+    for (int i = 0; i < 2; ++i) pb.rayPath[i] = (int *)take(sizeof(int) * n);
+    pb.hits = (uint32_t *)take(sizeof(uint32_t) * 6 * n);
+    for (int m = 0; m < kMatQueues; ++m) pb.matQ[m] = (int *)take(sizeof(int) * n);
+    pb.shRays = (float *)take(sizeof(float) * 7 * n);
+    pb.shPath = (int *)take(sizeof(int) * n);
+    pb.Ld = (float *)take(sizeof(float) * kNLambda * n);
+    pb.occluded = (unsigned char *)take(size_t(n));
+    pb.counts = (int *)take(sizeof(int) * kCountStride * depthSlots);
+    pb.maxDepthSlots = depthSlots;
 }
 
-// ---- path <-> SoA
+// ---- queue push: one atomic per group of converged lanes
+__device__ __forceinline__ int QueuePush(int *counter) {
+    unsigned m = __activemask();
+    int lane = threadIdx.x & 31, leader = __ffs(m) - 1, base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(m, base, leader);
+    return base + __popc(m & ((1u << lane) - 1));
+}
+
 __device__ __forceinline__ void StoreRay(float *rays, int i, V3 o, V3 d, float tMax) {
     float *q = rays + 7ll * i;
     q[0] = o.x; q[1] = o.y; q[2] = o.z;
@@ -55,151 +75,169 @@ __device__ __forceinline__ void StoreRay(float *rays, int i, V3 o, V3 d, float t
     q[6] = tMax;
 }
 
-__device__ __forceinline__ void StorePath(const PathBuffers &pb, int i, const PathRegs &p, bool storeLd) {
+// ---- path <-> SoA (beta is handled by the kernels: it is not needed by every path)
+__device__ __forceinline__ void StoreHeader(const PassBuffers &pb, int i, const PathRegs &p) {
     const long long n = pb.n;
-    float *beta = pb.spec + i, *L = beta + kNLambda * n, *Ld = L + kNLambda * n;
-#pragma unroll
-    for (int k = 0; k < kNLambda; ++k) {
-        beta[k * n] = p.beta[k];
-        L[k * n] = p.L[k];
-    }
-    if (storeLd) {
-#pragma unroll
-        for (int k = 0; k < kNLambda; ++k) Ld[k * n] = p.Ld[k];
-    }
     float *s = pb.scalars + i;
     s[0 * n] = p.lambdaU;
     s[1 * n] = p.etaScale;
     s[2 * n] = p.pB;
-    s[3 * n] = p.filterWeight;
-    s[4 * n] = p.prev.pi.lo.x; s[5 * n] = p.prev.pi.lo.y; s[6 * n] = p.prev.pi.lo.z;
-    s[7 * n] = p.prev.pi.hi.x; s[8 * n] = p.prev.pi.hi.y; s[9 * n] = p.prev.pi.hi.z;
-    s[10 * n] = p.prev.n.x; s[11 * n] = p.prev.n.y; s[12 * n] = p.prev.n.z;
-    s[13 * n] = p.prev.ns.x; s[14 * n] = p.prev.ns.y; s[15 * n] = p.prev.ns.z;
+    s[3 * n] = p.prev.pi.lo.x; s[4 * n] = p.prev.pi.lo.y; s[5 * n] = p.prev.pi.lo.z;
+    s[6 * n] = p.prev.pi.hi.x; s[7 * n] = p.prev.pi.hi.y; s[8 * n] = p.prev.pi.hi.z;
+    s[9 * n] = p.prev.n.x; s[10 * n] = p.prev.n.y; s[11 * n] = p.prev.n.z;
+    s[12 * n] = p.prev.ns.x; s[13 * n] = p.prev.ns.y; s[14 * n] = p.prev.ns.z;
     int *q = pb.ints + i;
     q[0 * n] = p.sampleIndex;
     q[1 * n] = p.dimension;
     q[2 * n] = p.depth;
     q[3 * n] = (int)p.flags;
-    StoreRay(pb.rays, i, p.rayO, p.rayD, p.rayTMax);
-    StoreRay(pb.shadowRays, i, p.shO, p.shD, p.shTMax);
 }
 
-__device__ __forceinline__ void LoadPath(const PathBuffers &pb, int i, PathRegs &p, bool loadLd) {
+__device__ __forceinline__ void LoadHeader(const PassBuffers &pb, int i, PathRegs &p) {
     const long long n = pb.n;
-    const float *beta = pb.spec + i, *L = beta + kNLambda * n, *Ld = L + kNLambda * n;
-#pragma unroll
-    for (int k = 0; k < kNLambda; ++k) {
-        p.beta[k] = beta[k * n];
-        p.L[k] = L[k * n];
-    }
-#pragma unroll
-    for (int k = 0; k < kNLambda; ++k) p.Ld[k] = loadLd ? Ld[k * n] : 0.f;
     const float *s = pb.scalars + i;
     p.lambdaU = s[0 * n];
     p.etaScale = s[1 * n];
     p.pB = s[2 * n];
-    p.filterWeight = s[3 * n];
-    p.prev.pi.lo = mk(s[4 * n], s[5 * n], s[6 * n]);
-    p.prev.pi.hi = mk(s[7 * n], s[8 * n], s[9 * n]);
-    p.prev.n = mk(s[10 * n], s[11 * n], s[12 * n]);
-    p.prev.ns = mk(s[13 * n], s[14 * n], s[15 * n]);
+    p.prev.pi.lo = mk(s[3 * n], s[4 * n], s[5 * n]);
+    p.prev.pi.hi = mk(s[6 * n], s[7 * n], s[8 * n]);
+    p.prev.n = mk(s[9 * n], s[10 * n], s[11 * n]);
+    p.prev.ns = mk(s[12 * n], s[13 * n], s[14 * n]);
     const int *q = pb.ints + i;
     p.sampleIndex = q[0 * n];
     p.dimension = q[1 * n];
     p.depth = q[2 * n];
     p.flags = (uint32_t)q[3 * n];
-    const float *r = pb.rays + 7ll * i;
-    p.rayO = mk(r[0], r[1], r[2]);
-    p.rayD = mk(r[3], r[4], r[5]);
-    p.rayTMax = r[6];
-    p.shTMax = -1.f;
-    p.shO = mk(0, 0, 0);
-    p.shD = mk(0, 0, 0);
+    p.filterWeight = 1.f;
 }
 
-__device__ __forceinline__ void CountRays(bool closest, bool shadow, unsigned long long *counters) {
-    unsigned c = __ballot_sync(0xffffffffu, closest), s = __ballot_sync(0xffffffffu, shadow);
-    if ((threadIdx.x & 31) == 0) {
-        if (c) atomicAdd(counters + 0, (unsigned long long)__popc(c));
-        if (s) atomicAdd(counters + 1, (unsigned long long)__popc(s));
+// IO of ShadeVertex on the device: radiance goes straight to the path's L, a light sample goes to a
+// fresh slot of the shadow queue of this depth.
+struct DevIO {
+    const PassBuffers &pb;
+    int path;
+    int *nShadow;
+    int slot;
+    __device__ DevIO(const PassBuffers &b, int pathId, int *shadowCount) : pb(b), path(pathId), nShadow(shadowCount), slot(-1) {}
+    __device__ __forceinline__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
+    __device__ __forceinline__ void ShadowBegin() { slot = QueuePush(nShadow); }
+    __device__ __forceinline__ void SetLd(int k, float v) { pb.Ld[(long long)k * pb.n + slot] = v; }
+    __device__ __forceinline__ void ShadowEnd(bool valid, V3 o, V3 d, float tMax) {
+        StoreRay(pb.shRays, slot, o, d, valid ? tMax : -1.f);
+        pb.shPath[slot] = valid ? path : -1;
     }
-}
+};
 
 // ---- camera rays: RayIntegrator::EvaluatePixelSample up to GenerateRay (cpu/integrators.cpp:228-262)
 __global__ void __launch_bounds__(kShadeBlock)
-GenerateKernel(RenderSceneDev rs, PathBuffers pb, int nPixels, int width, int nActive, int firstSample,
-               int sampleStride, unsigned long long *counters) {
+GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nActive, int firstSample,
+               int sampleStride) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool live = i < nActive;
-    if (live) {
-        int pix = i % nPixels, s = i / nPixels;
-        PathRegs p;
-        p.prev.pi.lo = p.prev.pi.hi = p.prev.n = p.prev.ns = mk(0, 0, 0);
-        p.shO = p.shD = mk(0, 0, 0);
-        GenerateCameraPath(rs, p, rs.film.x0 + pix % width, rs.film.y0 + pix / width,
-                           firstSample + s * sampleStride);
-        StorePath(pb, i, p, false);
-        pb.occluded[i] = 0;
+    if (i == 0) pb.counts[0] = nActive;  // ray queue of depth 0: one camera ray per path, slot = path
+    if (i >= nActive) return;
+    int pix = i % nPixels, s = i / nPixels;
+    PathRegs p;
+    GenerateCameraPath(rs, p, rs.film.x0 + pix % width, rs.film.y0 + pix / width, firstSample + s * sampleStride);
+    const long long n = pb.n;
+#pragma unroll
+    for (int k = 0; k < kNLambda; ++k) {
+        pb.beta[k * n + i] = 1.f;
+        pb.L[k * n + i] = 0.f;
     }
-    CountRays(live, false, counters);
+    StoreHeader(pb, i, p);
+    StoreRay(pb.rays[0], i, p.rayO, p.rayD, p.rayTMax);
+    pb.rayPath[0][i] = i;
+}
+
+// ---- hits -> material-sorted queues (the role of EnqueueWorkAfterIntersection, wavefront/intersect.h:67-170)
+__global__ void __launch_bounds__(256)
+ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int *counts = pb.counts + kCountStride * depth;
+    if (t >= counts[0]) return;
+    uint32_t slot = pb.hits[6ll * t];
+    if (slot == kMissTag) return;  // escaped: no infinite lights yet, the path ends
+    const PrimSlot *ps = reinterpret_cast<const PrimSlot *>(rs.prims) + slot;
+    int material = rs.meshes[ps->mesh].material;
+    uint32_t type = material >= 0 ? rs.materials[material].type : 0u;  // null material: any queue ends the path
+    if (type >= (uint32_t)kMatQueues) type = 0;
+    // per-type push: lanes of one type share an atomic
+    for (uint32_t m = 0; m < (uint32_t)kMatQueues; ++m)
+        if (type == m) pb.matQ[m][QueuePush(counts + 2 + m)] = t;
 }
 
 // ---- one path vertex: PathIntegrator::Li loop body (cpu/integrators.cpp:640-760)
+template <int MAT>
 __global__ void __launch_bounds__(kShadeBlock)
-ShadeKernel(RenderSceneDev rs, PathBuffers pb, int nPixels, int width, int nActive, unsigned long long *counters) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool nextRay = false, shadowRay = false;
-    if (i < nActive) {
-        uint32_t flags = (uint32_t)pb.ints[3ll * pb.n + i];
-        if (flags & (PF_ALIVE | PF_SHADOW_PENDING)) {
-            PathRegs p;
-            LoadPath(pb, i, p, (flags & PF_SHADOW_PENDING) != 0);
-            int pix = i % nPixels;
-            p.px = rs.film.x0 + pix % width;
-            p.py = rs.film.y0 + pix / width;
-            uint32_t hit[6];
-            const uint2 *h = reinterpret_cast<const uint2 *>(pb.hits + 6ll * i);
-            uint2 h0 = h[0], h1 = h[1], h2 = h[2];
-            hit[0] = h0.x; hit[1] = h0.y; hit[2] = h1.x; hit[3] = h1.y; hit[4] = h2.x; hit[5] = h2.y;
-            ShadeVertex(rs, p, hit, pb.occluded[i] != 0);
-            StorePath(pb, i, p, (p.flags & PF_SHADOW_PENDING) != 0);
-            nextRay = (p.flags & PF_ALIVE) != 0;
-            shadowRay = (p.flags & PF_SHADOW_PENDING) != 0;
-        }
+ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int *counts = pb.counts + kCountStride * depth;
+    if (t >= counts[2 + MAT]) return;
+    const int cur = depth & 1, nxt = cur ^ 1;
+    int q = pb.matQ[MAT][t];
+    int path = pb.rayPath[cur][q];
+    const long long n = pb.n;
+    PathRegs p;
+    LoadHeader(pb, path, p);
+#pragma unroll
+    for (int k = 0; k < kNLambda; ++k) p.beta[k] = pb.beta[k * n + path];
+    int pix = path % nPixels;
+    p.px = rs.film.x0 + pix % width;
+    p.py = rs.film.y0 + pix / width;
+    const float *r = pb.rays[cur] + 7ll * q;
+    p.rayO = mk(r[0], r[1], r[2]);
+    p.rayD = mk(r[3], r[4], r[5]);
+    p.rayTMax = r[6];
+    uint32_t hit[6];
+    const uint2 *h = reinterpret_cast<const uint2 *>(pb.hits + 6ll * q);
+    uint2 h0 = h[0], h1 = h[1], h2 = h[2];
+    hit[0] = h0.x; hit[1] = h0.y; hit[2] = h1.x; hit[3] = h1.y; hit[4] = h2.x; hit[5] = h2.y;
+    DevIO io(pb, path, counts + 1);
+    ShadeVertex<DevIO, MAT>(rs, p, hit, io);
+    if (p.flags & PF_ALIVE) {
+        int *next = pb.counts + kCountStride * (depth + 1);
+        int slot = QueuePush(next);
+        StoreRay(pb.rays[nxt], slot, p.rayO, p.rayD, p.rayTMax);
+        pb.rayPath[nxt][slot] = path;
+#pragma unroll
+        for (int k = 0; k < kNLambda; ++k) pb.beta[k * n + path] = p.beta[k];
+        StoreHeader(pb, path, p);
+    } else {
+        pb.ints[3 * n + path] = (int)p.flags;  // the finish kernel needs PF_TERMINATED_SECONDARY
     }
-    CountRays(nextRay, shadowRay, counters);
+}
+
+// ---- unoccluded light samples join the path's radiance (RecordShadowRayResult, wavefront/intersect.h:176-190)
+__global__ void __launch_bounds__(256)
+ResolveShadowKernel(PassBuffers pb, int depth) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= pb.counts[kCountStride * depth + 1]) return;
+    int path = pb.shPath[t];
+    if (path < 0 || pb.occluded[t]) return;
+    const long long n = pb.n;
+#pragma unroll
+    for (int k = 0; k < kNLambda; ++k) pb.L[k * n + path] += pb.Ld[k * n + t];
 }
 
 // ---- finished sample -> weighted sensor RGB (RGBFilm::AddSample, film.h:241-258)
 __global__ void __launch_bounds__(kShadeBlock)
-FinishKernel(RenderSceneDev rs, PathBuffers pb, int nPixels, int nActive) {
+FinishKernel(RenderSceneDev rs, PassBuffers pb, int nActive) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nActive) return;
     const long long n = pb.n;
-    PathRegs p;
-    const float *L = pb.spec + kNLambda * n + i, *Ld = L + kNLambda * n;
-    p.flags = (uint32_t)pb.ints[3 * n + i];
-    bool pending = (p.flags & PF_SHADOW_PENDING) != 0;
-#pragma unroll
-    for (int k = 0; k < kNLambda; ++k) {
-        p.L[k] = L[k * n];
-        p.Ld[k] = pending ? Ld[k * n] : 0.f;
-    }
-    p.lambdaU = pb.scalars[i];
-    p.filterWeight = pb.scalars[3 * n + i];
+    const float *L = pb.L + i;
     float rgbw[4];
-    FinishPath(rs, p, pb.occluded[i] != 0, rgbw);
+    FinishPath(rs, pb.scalars[i], (uint32_t)pb.ints[3 * n + i], 1.f, [&](int k) { return L[k * n]; }, rgbw);
     reinterpret_cast<float4 *>(pb.rgbw)[i] = make_float4(rgbw[0], rgbw[1], rgbw[2], rgbw[3]);
 }
 
 // ---- film: one thread per pixel adds the pass's samples in sample order, as the CPU film does for
 // a pixel (each pixel is owned by one thread there too), so the double sums are the reference's.
-__global__ void FilmAddKernel(PathBuffers pb, int nPixels, int nSamplesInPass, double *film) {
+__global__ void FilmAddKernel(PassBuffers pb, int nPixels, int nSamplesInPass, double *film) {
     int pix = blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= nPixels) return;
-    double4 *dst = reinterpret_cast<double4 *>(film) + pix;
-    double2 a = reinterpret_cast<double2 *>(dst)[0], b = reinterpret_cast<double2 *>(dst)[1];
+    double2 *dst = reinterpret_cast<double2 *>(film) + 2ll * pix;
+    double2 a = dst[0], b = dst[1];
     for (int s = 0; s < nSamplesInPass; ++s) {
         float4 v = reinterpret_cast<const float4 *>(pb.rgbw)[(long long)s * nPixels + pix];
         a.x += v.x;
@@ -207,8 +245,8 @@ __global__ void FilmAddKernel(PathBuffers pb, int nPixels, int nSamplesInPass, d
         b.x += v.z;
         b.y += v.w;
     }
-    reinterpret_cast<double2 *>(dst)[0] = a;
-    reinterpret_cast<double2 *>(dst)[1] = b;
+    dst[0] = a;
+    dst[1] = b;
 }
 
 // RGBFilm::GetPixelRGB (film.h:261-277)
@@ -228,30 +266,64 @@ __global__ void FilmImageKernel(FilmDev film, const double *acc, int nPixels, fl
     rgb[3ll * pix + 2] = m[6] * r + m[7] * g + m[8] * b;
 }
 
+__global__ void SumCountsKernel(PassBuffers pb, int depths, unsigned long long *totals) {
+    unsigned long long c = 0, s = 0;
+    for (int d = 0; d < depths; ++d) {
+        c += (unsigned long long)pb.counts[kCountStride * d];
+        s += (unsigned long long)pb.counts[kCountStride * d + 1];
+    }
+    totals[0] += c;
+    totals[1] += s;
+}
+
 static inline int Blocks(long long n, int b) { return (int)((n + b - 1) / b); }
 
-cudaError_t LaunchGenerate(const RenderSceneDev &rs, const PathBuffers &pb, int nPixels, int width, int nActive,
-                           int firstSample, int sampleStride, unsigned long long *counters, cudaStream_t stream) {
+cudaError_t LaunchGenerate(const RenderSceneDev &rs, const PassBuffers &pb, int nPixels, int width, int nActive,
+                           int firstSample, int sampleStride, cudaStream_t stream) {
     GenerateKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, nPixels, width, nActive,
-                                                                             firstSample, sampleStride, counters);
+                                                                             firstSample, sampleStride);
     return cudaGetLastError();
 }
-cudaError_t LaunchShade(const RenderSceneDev &rs, const PathBuffers &pb, int nPixels, int width, int nActive,
-                        unsigned long long *counters, cudaStream_t stream) {
-    ShadeKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, nPixels, width, nActive, counters);
+cudaError_t LaunchClassify(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive,
+                           cudaStream_t stream) {
+    ClassifyKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth);
     return cudaGetLastError();
 }
-cudaError_t LaunchFinish(const RenderSceneDev &rs, const PathBuffers &pb, int nPixels, int nActive,
-                         cudaStream_t stream) {
-    FinishKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, nPixels, nActive);
+cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width,
+                        int nActive, uint32_t matMask, cudaStream_t stream, int *launches) {
+    int grid = Blocks(nActive, kShadeBlock);
+    if (matMask & 1u) {
+        ShadeKernel<MAT_DIFFUSE><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
+        ++*launches;
+    }
+    if (matMask & 2u) {
+        ShadeKernel<MAT_CONDUCTOR><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
+        ++*launches;
+    }
+    if (matMask & 4u) {
+        ShadeKernel<MAT_DIELECTRIC><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
+        ++*launches;
+    }
     return cudaGetLastError();
 }
-cudaError_t LaunchFilmAdd(const PathBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream) {
+cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {
+    ResolveShadowKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(pb, depth);
+    return cudaGetLastError();
+}
+cudaError_t LaunchFinish(const RenderSceneDev &rs, const PassBuffers &pb, int nActive, cudaStream_t stream) {
+    FinishKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, nActive);
+    return cudaGetLastError();
+}
+cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream) {
     FilmAddKernel<<<Blocks(nPixels, 128), 128, 0, stream>>>(pb, nPixels, nSamplesInPass, film);
     return cudaGetLastError();
 }
 cudaError_t LaunchFilmImage(const FilmDev &film, const double *acc, int nPixels, float *rgb, cudaStream_t stream) {
     FilmImageKernel<<<Blocks(nPixels, 128), 128, 0, stream>>>(film, acc, nPixels, rgb);
+    return cudaGetLastError();
+}
+cudaError_t LaunchSumCounts(const PassBuffers &pb, int depths, unsigned long long *totals, cudaStream_t stream) {
+    SumCountsKernel<<<1, 1, 0, stream>>>(pb, depths, totals);
     return cudaGetLastError();
 }
 

@@ -25,8 +25,9 @@ struct b200pt_render {
     double *dFilm = nullptr;
     float *dImage = nullptr;
     void *dPaths = nullptr;
-    PathBuffers pb{};
+    PassBuffers pb{};
     long long pathCap = 0;
+    uint32_t matMask = 0;                     // material types present in the scene
     unsigned long long *dCounters = nullptr;  // [0] closest rays, [1] shadow rays
     int *dRayCounter = nullptr;               // work counter of the persistent traversal kernel
     int nPixels = 0;
@@ -98,6 +99,10 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     r->dev.lights = (const LightDev *)r->dLights;
     r->dev.meshes = (const MeshAttrDev *)r->dMeshes;
     r->dev.prims = scene->dev.prims;
+    for (const MaterialDev &m : r->host.materials) r->matMask |= 1u << m.type;
+    for (const MeshAttrDev &m : r->host.meshes)
+        if (m.material < 0) r->matMask |= 1u;  // null materials go through the diffuse queue, which ends the path
+    if (r->matMask == 0) r->matMask = 1;
     if (const char *v = getenv("B200PT_PASS_PATHS")) r->maxPathsPerPass = std::max(1ll, atoll(v));
     if (cudaMalloc((void **)&r->dFilm, sizeof(double) * 4 * r->nPixels) != cudaSuccess ||
         cudaMalloc((void **)&r->dImage, sizeof(float) * 3 * r->nPixels) != cudaSuccess ||
@@ -137,55 +142,62 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
         ctx->err = "render_run: film too large for one pass";
         return B200PT_ERR_INVALID;
     }
+    const DeviceScene &sc = r->scene->dev;
+    const int stackDepth = int(sc.maxDepth) + 1;
+    const int maxDepth = r->dev.integrator.maxDepth;
+    const int depthSlots = maxDepth + 2;
     if (need > r->pathCap) {
         B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         cudaFree(r->dPaths);
         r->dPaths = nullptr;
         r->pathCap = 0;
-        if (cudaMalloc(&r->dPaths, PathBufferBytes(need)) != cudaSuccess) {
+        if (cudaMalloc(&r->dPaths, PassBufferBytes(need, depthSlots)) != cudaSuccess) {
             (void)cudaGetLastError();
             ctx->err = "render_run: out of device memory for the path buffers";
             return B200PT_ERR_NOMEM;
         }
-        CarvePathBuffers(r->dPaths, need, r->pb);
+        CarvePassBuffers(r->dPaths, need, depthSlots, r->pb);
         r->pathCap = need;
     }
-    const DeviceScene &sc = r->scene->dev;
-    const int stackDepth = int(sc.maxDepth) + 1;
-    const int maxDepth = r->dev.integrator.maxDepth;
-    uint32_t launches = 0;
+    const PassBuffers &pb = r->pb;
+    int launches = 0;
     B2_CUDA(ctx, cudaMemsetAsync(r->dCounters, 0, 4 * sizeof(unsigned long long), ctx->stream));
     B2_CUDA(ctx, cudaEventRecord(r->ev0, ctx->stream));
     for (int done = 0; done < n_samples; done += perPass) {
         int ns = std::min(perPass, n_samples - done);
         int nActive = ns * nPix;
-        B2_CUDA(ctx, LaunchGenerate(r->dev, r->pb, nPix, width, nActive, first_sample + done * sample_stride,
-                                    sample_stride, r->dCounters, ctx->stream));
+        B2_CUDA(ctx, cudaMemsetAsync(pb.counts, 0, sizeof(int) * kCountStride * depthSlots, ctx->stream));
+        B2_CUDA(ctx, LaunchGenerate(r->dev, pb, nPix, width, nActive, first_sample + done * sample_stride,
+                                    sample_stride, ctx->stream));
         ++launches;
-        // vertex j: closest hit of the path ray, visibility of the shadow ray issued at vertex j-1, shade.
-        // Vertex maxDepth only collects emission and the last shadow ray (cpu/integrators.cpp:690-692).
+        // vertex j: closest hit of the rays in queue j -> material queues -> shading (next rays into queue
+        // j+1, light samples into the shadow queue) -> visibility of the light samples -> radiance.
+        // Vertex maxDepth only collects emission (cpu/integrators.cpp:690-692).
         for (int j = 0; j <= maxDepth; ++j) {
-            B2_CUDA(ctx, LaunchTraversePersist(sc, r->pb.rays, nActive, (b200pt_hit *)r->pb.hits, nullptr, false,
+            const int *nRays = pb.counts + kCountStride * j, *nShadow = nRays + 1;
+            B2_CUDA(ctx, LaunchTraversePersist(sc, pb.rays[j & 1], nActive, (b200pt_hit *)pb.hits, nullptr, false,
                                                r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
-                                               ctx->nodeMin, ctx->stream, true));
-            ++launches;
-            if (j > 0) {
-                B2_CUDA(ctx, LaunchTraversePersist(sc, r->pb.shadowRays, nActive, nullptr, r->pb.occluded, true,
-                                                   r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
-                                                   ctx->nodeMin, ctx->stream, false));
-                ++launches;
+                                               ctx->nodeMin, ctx->stream, true, nRays));
+            B2_CUDA(ctx, LaunchClassify(r->dev, pb, j, nActive, ctx->stream));
+            launches += 2;
+            B2_CUDA(ctx, LaunchShade(r->dev, pb, j, nPix, width, nActive, r->matMask, ctx->stream, &launches));
+            if (j < maxDepth) {
+                B2_CUDA(ctx, LaunchTraversePersist(sc, pb.shRays, nActive, nullptr, pb.occluded, true, r->dRayCounter,
+                                                   nullptr, ctx->smCount, stackDepth, ctx->refillMin, ctx->nodeMin,
+                                                   ctx->stream, false, nShadow));
+                B2_CUDA(ctx, LaunchResolveShadows(pb, j, nActive, ctx->stream));
+                launches += 2;
             }
-            B2_CUDA(ctx, LaunchShade(r->dev, r->pb, nPix, width, nActive, r->dCounters, ctx->stream));
-            ++launches;
         }
-        B2_CUDA(ctx, LaunchFinish(r->dev, r->pb, nPix, nActive, ctx->stream));
-        B2_CUDA(ctx, LaunchFilmAdd(r->pb, nPix, ns, r->dFilm, ctx->stream));
-        launches += 2;
+        B2_CUDA(ctx, LaunchFinish(r->dev, pb, nActive, ctx->stream));
+        B2_CUDA(ctx, LaunchFilmAdd(pb, nPix, ns, r->dFilm, ctx->stream));
+        B2_CUDA(ctx, LaunchSumCounts(pb, maxDepth + 1, r->dCounters, ctx->stream));
+        launches += 3;
     }
     B2_CUDA(ctx, cudaEventRecord(r->ev1, ctx->stream));
     r->timed = true;
     r->stats.samples = (uint64_t)n_samples * nPix;
-    r->stats.kernel_launches = launches;
+    r->stats.kernel_launches = (uint32_t)launches;
     return B200PT_OK;
 }
 

@@ -80,8 +80,21 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     out.materials.resize(d->n_materials);
     for (uint32_t i = 0; i < d->n_materials; ++i) {
         const b200pt_material &m = d->materials[i];
-        if (m.type != B200PT_MAT_DIFFUSE) return bad("unsupported material type (diffuse is implemented)");
-        if (!specOk(m.spectrum[0])) return bad("material spectrum index out of range");
+        auto opt = [&](int32_t sp) { return sp < 0 || specOk(sp); };
+        switch (m.type) {
+        case B200PT_MAT_DIFFUSE:
+        case B200PT_MAT_DIELECTRIC:
+            if (!specOk(m.spectrum[0])) return bad("material spectrum index out of range");
+            break;
+        case B200PT_MAT_CONDUCTOR:  // eta + k, or reflectance (materials.h:498-507)
+            if (!opt(m.spectrum[0]) || !opt(m.spectrum[1]) || !opt(m.spectrum[2]))
+                return bad("material spectrum index out of range");
+            if (m.spectrum[0] >= 0 ? m.spectrum[1] < 0 : m.spectrum[2] < 0)
+                return bad("conductor needs eta and k, or reflectance");
+            break;
+        default:
+            return bad("unsupported material type (diffuse, conductor, dielectric are implemented)");
+        }
         out.materials[i].type = m.type;
         std::memcpy(out.materials[i].spectrum, m.spectrum, 16);
         std::memcpy(out.materials[i].params, m.params, 32);

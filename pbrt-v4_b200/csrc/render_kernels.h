@@ -1,4 +1,4 @@
-// render_kernels.h - launchers of the render-path kernels (render.cu) and the per-pass path buffers.
+// render_kernels.h - launchers of the render-path kernels (render.cu) and the per-pass buffers.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -8,33 +8,54 @@
 
 namespace b200pt {
 
+constexpr int kPathScalars = 15;  // lambdaU, etaScale, pB, prev{pi.lo, pi.hi, n, ns}
+constexpr int kPathInts = 4;      // sampleIndex, dimension, depth, flags
+constexpr int kMatQueues = 4;     // one shading queue per MaterialType
+constexpr int kCountStride = 8;   // ints per depth in PassBuffers::counts
+
 // One pass = nPixels x nSamplesInPass paths; path i is pixel i % nPixels, sample slot i / nPixels.
-// Spectral arrays are [k][path] and scalar state [field][path], so a warp's accesses coalesce.
-struct PathBuffers {
+// Path state is indexed by path id and laid out [field][path] so a warp's accesses coalesce; the
+// queues (rays, hits, shadow rays, material queues) are dense and indexed by queue slot.  Queue
+// lengths live on the device (counts): the host never reads them inside a pass, launches are sized
+// for the worst case and threads past the length exit (as the reference's wavefront does,
+// wavefront/integrator.cpp:403-406 "maxQueueSize").
+struct PassBuffers {
     int n;                 // capacity in paths
-    float *spec;           // 3 x 31 x n : beta, L, Ld
+    // ---- per path
+    float *beta;           // 31 x n
+    float *L;              // 31 x n   radiance so far
     float *scalars;        // kPathScalars x n
     int *ints;             // kPathInts x n
-    float *rays;           // n x 7  {o, d, tMax}; tMax < 0 = no ray
-    float *shadowRays;     // n x 7
-    uint32_t *hits;        // n x 6  internal record {slot, t, b0, b1, b2, 0}
+    float *rgbw;           // n x 4    finished sample: weight * sensor rgb, weight
+    // ---- per queue slot
+    float *rays[2];        // n x 7 {o, d, tMax}, current / next depth
+    int *rayPath[2];       // n     path id of the ray in that slot
+    uint32_t *hits;        // n x 6 internal record {slot, t, b0, b1, b2, 0}
+    int *matQ[kMatQueues]; // n     ray slots whose hit has material type m
+    float *shRays;         // n x 7 shadow rays
+    int *shPath;           // n     path id, -1 = void slot
+    float *Ld;             // 31 x n  contribution to add when unoccluded (already x beta)
     unsigned char *occluded;  // n
-    float *rgbw;           // n x 4  finished sample: weight * sensor rgb, weight
+    // ---- queue lengths: counts[kCountStride * depth + {0 rays, 1 shadow, 2.. material queues}]
+    int *counts;
+    int maxDepthSlots;
 };
-constexpr int kPathScalars = 16;  // lambdaU, etaScale, pB, filterWeight, prev{pi.lo, pi.hi, n, ns}
-constexpr int kPathInts = 4;      // sampleIndex, dimension, depth, flags
 
-size_t PathBufferBytes(long long n);
-void CarvePathBuffers(void *base, long long n, PathBuffers &pb);
+size_t PassBufferBytes(long long n, int depthSlots);
+void CarvePassBuffers(void *base, long long n, int depthSlots, PassBuffers &pb);
 
-// counters: [0] closest rays issued, [1] shadow rays issued
-cudaError_t LaunchGenerate(const RenderSceneDev &rs, const PathBuffers &pb, int nPixels, int width, int nActive,
-                           int firstSample, int sampleStride, unsigned long long *counters, cudaStream_t stream);
-cudaError_t LaunchShade(const RenderSceneDev &rs, const PathBuffers &pb, int nPixels, int width, int nActive,
-                        unsigned long long *counters, cudaStream_t stream);
-cudaError_t LaunchFinish(const RenderSceneDev &rs, const PathBuffers &pb, int nPixels, int nActive,
-                         cudaStream_t stream);
-cudaError_t LaunchFilmAdd(const PathBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream);
+cudaError_t LaunchGenerate(const RenderSceneDev &rs, const PassBuffers &pb, int nPixels, int width, int nActive,
+                           int firstSample, int sampleStride, cudaStream_t stream);
+cudaError_t LaunchClassify(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive,
+                           cudaStream_t stream);
+// matMask: bit m set = material type m occurs in the scene (its queue is shaded)
+cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width,
+                        int nActive, uint32_t matMask, cudaStream_t stream, int *launches);
+cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream);
+cudaError_t LaunchFinish(const RenderSceneDev &rs, const PassBuffers &pb, int nActive, cudaStream_t stream);
+cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream);
 cudaError_t LaunchFilmImage(const FilmDev &film, const double *acc, int nPixels, float *rgb, cudaStream_t stream);
+// sums counts over depths into totals[0] (closest rays) and totals[1] (shadow rays)
+cudaError_t LaunchSumCounts(const PassBuffers &pb, int depths, unsigned long long *totals, cudaStream_t stream);
 
 }  // namespace b200pt

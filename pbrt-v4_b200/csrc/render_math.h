@@ -37,6 +37,10 @@ B2_HD float SumOfProductsF(float a, float b, float c, float d) {  // util/math.h
 }
 B2_HD float Dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }  // util/vecmath.h:966-969
 B2_HD float AbsDot(V3 a, V3 b) { return fabsf(Dot(a, b)); }
+// Dot with a Normal3f on either side is a different expression in the reference
+// (util/vecmath.h:1059-1077): FMA(n.x, v.x, SumOfProducts(n.y, v.y, n.z, v.z)).
+B2_HD float DotN(V3 n, V3 v) { return FMAf(n.x, v.x, SumOfProductsF(n.y, v.y, n.z, v.z)); }
+B2_HD float AbsDotN(V3 n, V3 v) { return fabsf(DotN(n, v)); }
 B2_HD V3 Cross(V3 v, V3 w) {
     return mk(DiffOfProducts(v.y, w.z, v.z, w.y), DiffOfProducts(v.z, w.x, v.x, w.z),
               DiffOfProducts(v.x, w.y, v.y, w.x));
@@ -45,7 +49,7 @@ B2_HD float LengthSquared(V3 v) { return SqrF(v.x) + SqrF(v.y) + SqrF(v.z); }
 B2_HD float Length(V3 v) { return sqrtf(LengthSquared(v)); }
 B2_HD V3 Normalize(V3 v) { return v / Length(v); }
 B2_HD V3 Abs(V3 v) { return mk(fabsf(v.x), fabsf(v.y), fabsf(v.z)); }
-B2_HD V3 FaceForward(V3 n, V3 v) { return (Dot(n, v) < 0.f) ? -n : n; }
+B2_HD V3 FaceForward(V3 n, V3 v) { return (DotN(n, v) < 0.f) ? -n : n; }  // one side is a Normal3f at every use
 B2_HD float Lerp(float t, float a, float b) { return (1 - t) * a + t * b; }
 B2_HD float Clampf(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
 B2_HD float SafeSqrt(float x) { return sqrtf(fmaxf(0.f, x)); }
@@ -112,9 +116,9 @@ B2_HD V3 Err(const P3i &p) { return mk((p.hi.x - p.lo.x) / 2, (p.hi.y - p.lo.y) 
 
 // OffsetRayOrigin (ray.h:78-95)
 B2_HD V3 OffsetRayOrigin(const P3i &pi, V3 n, V3 w) {
-    float d = Dot(Abs(n), Err(pi));
+    float d = DotN(Abs(n), Err(pi));
     V3 offset = d * n;
-    if (Dot(w, n) < 0) offset = -offset;
+    if (DotN(n, w) < 0) offset = -offset;
     V3 po = Mid(pi) + offset;
     if (offset.x > 0) po.x = NextUp(po.x); else if (offset.x < 0) po.x = NextDown(po.x);
     if (offset.y > 0) po.y = NextUp(po.y); else if (offset.y < 0) po.y = NextDown(po.y);

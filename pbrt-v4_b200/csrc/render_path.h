@@ -1,16 +1,27 @@
 // render_path.h - one path in registers and the steps the kernels apply to it (included by
 // render_shade.h).  GenerateCameraPath = RayIntegrator::EvaluatePixelSample up to the camera ray
 // (cpu/integrators.cpp:228-262); ShadeVertex = one iteration of PathIntegrator::Li's loop
-// (cpu/integrators.cpp:640-760) with SampleLd (:764-805) split at the shadow ray, whose
-// visibility comes back from the any-hit kernel before the next step; FinishPath = film AddSample.
+// (cpu/integrators.cpp:640-760) with SampleLd (:764-805) split at the shadow ray: the contribution
+// goes to a shadow-queue slot and is added to L when the any-hit kernel finds the ray unoccluded
+// (the reference's wavefront does the same: wavefront/intersect.h RecordShadowRayResult);
+// FinishPath = the film's AddSample.
+//
+// Spectral work is written as streams over k = 0..30 with the wavelength carried along a
+// recurrence (LambdaIter), never as arrays of 31 that must stay live across the whole step: only
+// beta[31] lives in registers; L and the pending Ld are reached through the IO object (global
+// memory on the device, plain arrays in tests/native/rendercheck.cpp).
 #pragma once
+#include "render_bsdf.h"
 
 namespace b200pt {
 
-enum : uint32_t { PF_ALIVE = 1u, PF_SPECULAR = 2u, PF_ANY_NONSPECULAR = 4u, PF_SHADOW_PENDING = 8u };
+enum : uint32_t {
+    PF_ALIVE = 1u, PF_SPECULAR = 2u, PF_ANY_NONSPECULAR = 4u,
+    PF_TERMINATED_SECONDARY = 16u  // SampledWavelengths::TerminateSecondary happened (util/spectrum.h:346-353)
+};
 
 struct PathRegs {
-    float beta[kNLambda], L[kNLambda], Ld[kNLambda];
+    float beta[kNLambda];
     float lambdaU;
     int px, py, sampleIndex, dimension, depth;
     uint32_t flags;
@@ -18,8 +29,16 @@ struct PathRegs {
     LightCtx prev;
     V3 rayO, rayD;
     float rayTMax;
-    V3 shO, shD;
-    float shTMax;
+};
+
+// lambda_k of SampledWavelengths::SampleUniform (util/spectrum.h:318-336), one at a time
+struct LambdaIter {
+    float lam;
+    B2_HD explicit LambdaIter(float u) : lam(Lerp(u, kLambdaMin, kLambdaMax)) {}
+    B2_HD void Next() {
+        lam = lam + (kLambdaMax - kLambdaMin) / kNLambda;
+        if (lam > kLambdaMax) lam = kLambdaMin + (lam - kLambdaMax);
+    }
 };
 
 B2_HD ZSobol SamplerFor(const RenderSceneDev &rs, const PathRegs &p) {
@@ -49,54 +68,102 @@ B2_HD void GenerateCameraPath(const RenderSceneDev &rs, PathRegs &p, int px, int
     p.dimension = s.dimension;
     GeneratePerspectiveRay(rs.camera, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
     p.rayTMax = INFINITY;
-    for (int k = 0; k < kNLambda; ++k) {
-        p.beta[k] = 1.f;
-        p.L[k] = 0.f;
-        p.Ld[k] = 0.f;
-    }
+#pragma unroll
+    for (int k = 0; k < kNLambda; ++k) p.beta[k] = 1.f;
     p.depth = 0;
     p.flags = PF_ALIVE;
     p.etaScale = 1.f;
     p.pB = 0.f;
-    p.shTMax = -1.f;
+    p.prev.pi.lo = p.prev.pi.hi = p.prev.n = p.prev.ns = mk(0, 0, 0);
 }
 
 B2_HD void KillPath(PathRegs &p) {
     p.flags &= ~PF_ALIVE;
-    p.rayTMax = -1.f;  // a ray with tMax < 0 fails the root box test: the traversal kernel drops it at once
+    p.rayTMax = -1.f;
+}
+
+// Material::GetBxDF for the surface (materials.h: Diffuse 430-476, Conductor 491-509, Dielectric 183-203)
+// MAT >= 0: the caller knows the material type (a material-sorted queue); the constant lets the
+// compiler drop the other models from that kernel.
+template <int MAT>
+B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lambda0, PathRegs &p) {
+    Bsdf b;
+    b.type = MAT >= 0 ? uint32_t(MAT) : mat.type;
+    b.tr = TRDist{0, 0};
+    b.eta = 1;
+    b.specA = mat.spectrum[0];
+    b.specB = -1;
+    if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC) {
+        float ur = mat.params[0], vr = mat.params[1];
+        if (mat.params[2] != 0) {  // remaproughness: RoughnessToAlpha = sqrt
+            ur = sqrtf(ur);
+            vr = sqrtf(vr);
+        }
+        b.tr = MakeTR(ur, vr);
+    }
+    if (b.type == MAT_CONDUCTOR) {
+        if (mat.spectrum[0] >= 0) {
+            b.specA = mat.spectrum[0];
+            b.specB = mat.spectrum[1];
+        } else {
+            b.specA = mat.spectrum[2];  // reflectance; k derived per wavelength
+            b.specB = -1;
+        }
+    }
+    if (b.type == MAT_DIELECTRIC) {
+        float e = SpectrumAt(rs.spectra[mat.spectrum[0]], lambda0);
+        if (mat.params[3] == 0) p.flags |= PF_TERMINATED_SECONDARY;  // eta is not a ConstantSpectrum
+        if (e == 0) e = 1;
+        b.eta = e;
+    }
+    return b;
+}
+
+// f_k: the per-wavelength factor applied to the scalar evaluation `e` (see BsdfEval)
+B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval &e, float lam) {
+    switch (e.kind) {
+    case 1: return e.scale;
+    case 2: return Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, 1) * e.scale;  // DiffuseMaterial clamps R
+    case 3:
+    case 4: {
+        float etaK, kK;
+        if (b.specB >= 0) {
+            etaK = SpectrumAt(rs.spectra[b.specA], lam);
+            kK = SpectrumAt(rs.spectra[b.specB], lam);
+        } else {  // materials.h:503-507
+            float r = Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, .9999f);
+            etaK = 1.f;
+            kK = 2 * sqrtf(r) / sqrtf(fmaxf(0.f, 1 - r));
+        }
+        float F = FrComplex(e.cosF, etaK, kK);
+        return e.kind == 3 ? (e.D * F) * e.G / e.denom : F / e.denom;
+    }
+    }
+    return 0.f;
 }
 
 // One path vertex.  `hit` is the internal record {slot, t, b0, b1, b2} of the closest-hit kernel for
-// p.ray; `prevOccluded` the any-hit answer for the shadow ray issued at the previous vertex.
-B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit[6], bool prevOccluded) {
-    // ---- finish SampleLd of the previous vertex: L += beta * Ld if unoccluded (cpu/integrators.cpp:795-804)
-    if (p.flags & PF_SHADOW_PENDING) {
-        if (!prevOccluded)
-            for (int k = 0; k < kNLambda; ++k) p.L[k] += p.Ld[k];
-        p.flags &= ~PF_SHADOW_PENDING;
-    }
-    p.shTMax = -1.f;
-    if (!(p.flags & PF_ALIVE)) return;
-
+// p.ray.  IO: AddL(k, v) adds to the path's radiance; ShadowBegin() / SetLd(k, v) / ShadowEnd(valid,
+// o, d, tMax) record a light sample whose visibility is still unknown.
+template <class IO, int MAT = -1>
+B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit[6], IO &io) {
     if (hit[0] == kMissTag) {  // no infinite lights yet: an escaped ray adds nothing (cpu/integrators.cpp:645-662)
         KillPath(p);
         return;
     }
-    float lambda[kNLambda];
-    SampleWavelengths(p.lambdaU, lambda);
     uint32_t slot = hit[0];
     float b0, b1, b2;
     memcpy(&b0, &hit[2], 4);
     memcpy(&b1, &hit[3], 4);
     memcpy(&b2, &hit[4], 4);
     TriVerts tv = LoadTri(rs.prims, slot);
-    const MeshAttrDev &mesh = rs.meshes[tv.mesh];
+    const MeshAttrDev mesh = rs.meshes[tv.mesh];
     V3 wo = -p.rayD;
     SurfHit si = TriangleInteraction(tv, b0, b1, b2, wo, mesh.flipNormal != 0);
 
     // ---- emitted light at the hit (cpu/integrators.cpp:664-679)
     if (mesh.lightFirst >= 0) {
-        const LightDev &al = rs.lights[mesh.lightFirst + tv.tri];
+        const LightDev al = rs.lights[mesh.lightFirst + tv.tri];
         if (AreaLightEmits(al, si.n, wo)) {
             float w = 1.f;
             if (!(p.depth == 0 || (p.flags & PF_SPECULAR))) {
@@ -106,25 +173,31 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
                 w = PowerHeuristic(p.pB, p_l);
             }
             const SpectrumTable &sp = rs.spectra[al.spectrum];
-            for (int k = 0; k < kNLambda; ++k) p.L[k] += p.beta[k] * w * (al.scale * SpectrumAt(sp, lambda[k]));
+            LambdaIter li(p.lambdaU);
+#pragma unroll
+            for (int k = 0; k < kNLambda; ++k, li.Next()) {
+                float Le = al.scale * SpectrumAt(sp, li.lam);
+                if (Le != 0) io.AddL(k, p.beta[k] * w * Le);
+            }
         }
     }
 
-    // ---- BSDF (materials.h:430-476 DiffuseMaterial::GetBxDF)
+    // ---- BSDF
     if (mesh.material < 0) {  // interface material: skip the surface (cpu/integrators.cpp:683-688); not used yet
         KillPath(p);
         return;
     }
-    const MaterialDev &mat = rs.materials[mesh.material];
-    float R[kNLambda];
-    bool anyR = false;
-    {
-        const SpectrumTable &sp = rs.spectra[mat.spectrum[0]];
-        for (int k = 0; k < kNLambda; ++k) {
-            R[k] = Clampf(SpectrumAt(sp, lambda[k]), 0, 1);
-            anyR |= R[k] != 0;
-        }
+    const MaterialDev mat = rs.materials[mesh.material];
+    Bsdf bsdf = MakeBsdf<MAT>(rs, mat, LambdaIter(p.lambdaU).lam, p);
+    uint32_t bflags = BsdfFlags(bsdf);
+    if (bsdf.type == MAT_DIFFUSE) {  // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
+        bool anyR = false;
+        LambdaIter li(p.lambdaU);
+#pragma unroll
+        for (int k = 0; k < kNLambda; ++k, li.Next()) anyR |= Clampf(SpectrumAt(rs.spectra[bsdf.specA], li.lam), 0, 1) != 0;
+        if (!anyR) bflags = 0;
     }
+    if (rs.integrator.regularize && (p.flags & PF_ANY_NONSPECULAR)) BsdfRegularize(bsdf);
     // BSDF shading frame: Frame::FromXZ(Normalize(dpdus), ns) (bsdf.h:24-25)
     V3 fx = Normalize(si.dpdus), fz = si.ns, fy = Cross(fz, fx);
     V3 woL = mk(Dot(wo, fx), Dot(wo, fy), Dot(wo, fz));
@@ -135,32 +208,37 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
     }
     ZSobol s = SamplerFor(rs, p);
 
-    // ---- direct lighting (SampleLd, cpu/integrators.cpp:764-805); DiffuseBxDF flags: reflective only
-    if (anyR) {
+    // ---- direct lighting (SampleLd, cpu/integrators.cpp:764-805)
+    if (bflags & (BX_DIFFUSE | BX_GLOSSY)) {
         LightCtx ctx;
         ctx.pi = si.pi;
         ctx.n = si.n;
         ctx.ns = si.ns;
-        V3 nudged = OffsetRayOrigin(si.pi, si.n, wo);  // ctx.pi = intr.OffsetRayOrigin(intr.wo)
-        ctx.pi.lo = nudged;
-        ctx.pi.hi = nudged;
+        bool refl = (bflags & BX_REFLECTION) != 0, trans = (bflags & BX_TRANSMISSION) != 0;
+        if (refl != trans) {  // nudge to the side light can arrive from
+            V3 nudged = OffsetRayOrigin(si.pi, si.n, refl ? si.wo : -si.wo);
+            ctx.pi.lo = nudged;
+            ctx.pi.hi = nudged;
+        }
+        // SampleLd evaluates the BSDF with intr.wo (normalised); Sample_f below gets -ray.d as it is
+        V3 woLd = mk(Dot(si.wo, fx), Dot(si.wo, fy), Dot(si.wo, fz));
         float uL = ZSobolGet1D(s);
         float uLight0, uLight1;
         ZSobolGet2D(s, uLight0, uLight1);
         if (rs.nLights > 0) {
             // AliasTable::Sample (util/sampling.cpp:619-647) / UniformLightSampler (lightsamplers.h:33-53)
-            int nl = (int)rs.nLights, li;
+            int nl = (int)rs.nLights, lidx;
             float pmf;
             if (rs.integrator.lightSampler == 0) {
-                li = (int)fminf(uL * nl, (float)(nl - 1));
+                lidx = (int)fminf(uL * nl, (float)(nl - 1));
                 pmf = 1.f / nl;
             } else {
                 int offset = (int)fminf(uL * nl, (float)(nl - 1));
                 float up = fminf(uL * nl - offset, kOneMinusEps);
-                li = (up < rs.lights[offset].aliasQ) ? offset : rs.lights[offset].alias;
-                pmf = rs.lights[li].aliasP;
+                lidx = (up < rs.lights[offset].aliasQ) ? offset : rs.lights[offset].alias;
+                pmf = rs.lights[lidx].aliasP;
             }
-            const LightDev &light = rs.lights[li];
+            const LightDev light = rs.lights[lidx];
             TriVerts lt = LoadTri(rs.prims, light.slot);
             ShapeSampleOut ss = SampleTriangleSolidAngle(lt, ctx, uLight0, uLight1, light.flipNormal != 0);
             V3 cp = Mid(ctx.pi);
@@ -169,65 +247,79 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
                 if (AreaLightEmits(light, ss.n, -wi)) {
                     float atten = 1.f;
                     if (light.cosFalloffEnd > 0) {  // ISET spread angle (lights.cpp:762-770)
-                        float cos_a = -Dot(wi, ss.n);
+                        float cos_a = -DotN(ss.n, wi);
                         float sin_a = SafeSqrt(1 - SqrF(cos_a));
                         float tan_a = sin_a / cos_a;
                         atten = fmaxf((1.0f - (light.tanFalloffEnd * tan_a)) * light.normalizeFalloffEnd, 0.0f);
                     }
                     V3 wiL = mk(Dot(wi, fx), Dot(wi, fy), Dot(wi, fz));
-                    bool sameHemi = wiL.z * woL.z > 0;
-                    if (woL.z != 0 && sameHemi) {
-                        float absCos = AbsDot(wi, si.ns);
+                    BsdfEval ev = (woLd.z == 0) ? ZeroEval() : BsdfF(bsdf, woLd, wiL);  // BSDF::f (bsdf.h:37-43)
+                    if (ev.kind != 0) {
+                        float absCos = AbsDotN(si.ns, wi);
                         float p_l = pmf * ss.pdf;
-                        float p_b = fabsf(wiL.z) * kInvPi;  // DiffuseBxDF::PDF
+                        float p_b = woLd.z == 0 ? 0.f : BsdfPDF(bsdf, woLd, wiL);
                         float w_l = PowerHeuristic(p_l, p_b);
                         const SpectrumTable &sp = rs.spectra[light.spectrum];
-                        bool any = false;
-                        for (int k = 0; k < kNLambda; ++k) {
-                            float Le = light.scale * SpectrumAt(sp, lambda[k]) * atten;
-                            float f = R[k] * kInvPi * absCos;
-                            float v = w_l * Le * f / p_l;
-                            p.Ld[k] = p.beta[k] * v;
-                            any |= (Le != 0) & (f != 0);
+                        bool anyL = false, anyF = false;
+                        io.ShadowBegin();
+                        LambdaIter li(p.lambdaU);
+#pragma unroll
+                        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+                            float Le = light.scale * SpectrumAt(sp, li.lam) * atten;
+                            float f = BsdfSpectral(rs, bsdf, ev, li.lam) * absCos;
+                            io.SetLd(k, p.beta[k] * (w_l * Le * f / p_l));
+                            anyL |= Le != 0;
+                            anyF |= f != 0;
                         }
-                        if (any) {
-                            // Unoccluded(intr, ls->pLight): intr.SpawnRayTo(pLight) (ray.h:106-111), tMax 1 - ShadowEpsilon
-                            V3 pf = OffsetRayOrigin(si.pi, si.n, Mid(ss.pi) - Mid(si.pi));
-                            V3 pt = OffsetRayOrigin(ss.pi, ss.n, pf - Mid(ss.pi));
-                            p.shO = pf;
-                            p.shD = pt - pf;
-                            p.shTMax = 1 - kShadowEpsilon;
-                            p.flags |= PF_SHADOW_PENDING;
-                        }
+                        // Unoccluded(intr, ls->pLight): intr.SpawnRayTo(pLight) (ray.h:106-111), tMax 1 - ShadowEpsilon
+                        V3 pf = OffsetRayOrigin(si.pi, si.n, Mid(ss.pi) - Mid(si.pi));
+                        V3 pt = OffsetRayOrigin(ss.pi, ss.n, pf - Mid(ss.pi));
+                        io.ShadowEnd(anyL && anyF, pf, pt - pf, 1 - kShadowEpsilon);
                     }
                 }
             }
         }
     }
 
-    // ---- sample the BSDF for the next direction (cpu/integrators.cpp:728-745; DiffuseBxDF::Sample_f bxdfs.h:44-56)
+    // ---- sample the BSDF for the next direction (cpu/integrators.cpp:728-745, BSDF::Sample_f bsdf.h:58-80)
     float uc = ZSobolGet1D(s);
-    (void)uc;
     float u0, u1;
     ZSobolGet2D(s, u0, u1);
     p.dimension = s.dimension;
-    if (woL.z == 0 || !anyR) {
+    if (woL.z == 0 || !(bflags & (BX_REFLECTION | BX_TRANSMISSION))) {
         KillPath(p);
         return;
     }
-    V3 wiL = SampleCosineHemisphere(u0, u1);
-    if (woL.z < 0) wiL.z *= -1;
-    float pdf = fabsf(wiL.z) * kInvPi;
-    if (pdf == 0 || wiL.z == 0) {
+    BsdfEval ev;
+    BsdfSample bs = BsdfSampleF(bsdf, woL, uc, u0, u1, ev);
+    if (!bs.ok || bs.pdf == 0 || bs.wi.z == 0) {
         KillPath(p);
         return;
     }
-    V3 wi = wiL.x * fx + wiL.y * fy + wiL.z * fz;  // Frame::FromLocal
-    float absCos = AbsDot(wi, si.ns);
-    for (int k = 0; k < kNLambda; ++k) p.beta[k] *= R[k] * kInvPi * absCos / pdf;
-    p.pB = pdf;
-    p.flags &= ~PF_SPECULAR;
-    p.flags |= PF_ANY_NONSPECULAR;
+    V3 wi = bs.wi.x * fx + bs.wi.y * fy + bs.wi.z * fz;  // Frame::FromLocal
+    float absCos = AbsDotN(si.ns, wi);
+#ifdef B2_PATH_DEBUG
+    printf("      sample: f0 %.9g absdot %.9g pdf %.9g eta %.9g woL %.9g %.9g %.9g\n", BsdfSpectral(rs, bsdf, ev, 500.f),
+           absCos, bs.pdf, bs.eta, woL.x, woL.y, woL.z);
+#endif
+    bool anyF = false;
+    {
+        LambdaIter li(p.lambdaU);
+#pragma unroll
+        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+            float f = BsdfSpectral(rs, bsdf, ev, li.lam);
+            anyF |= f != 0;
+            p.beta[k] *= f * absCos / bs.pdf;
+        }
+    }
+    if (!anyF) {  // !bs->f
+        KillPath(p);
+        return;
+    }
+    p.pB = bs.pdfIsProportional ? BsdfPDF(bsdf, woL, bs.wi) : bs.pdf;
+    bool specular = (bs.flags & BX_SPECULAR) != 0;
+    p.flags = specular ? (p.flags | PF_SPECULAR) : ((p.flags & ~PF_SPECULAR) | PF_ANY_NONSPECULAR);
+    if (bs.flags & BX_TRANSMISSION) p.etaScale *= SqrF(bs.eta);
     p.prev.pi = si.pi;
     p.prev.n = si.n;
     p.prev.ns = si.ns;
@@ -237,7 +329,11 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
 
     // ---- Russian roulette (cpu/integrators.cpp:748-756)
     float maxComp = p.beta[0] * p.etaScale;
+#pragma unroll
     for (int k = 1; k < kNLambda; ++k) maxComp = fmaxf(maxComp, p.beta[k] * p.etaScale);
+#ifdef B2_PATH_DEBUG
+    printf("      rr maxComp %.9g\n", maxComp);
+#endif
     if (maxComp < 1 && p.depth > 1) {
         float q = fmaxf(0.f, 1 - maxComp);
         s = SamplerFor(rs, p);
@@ -247,33 +343,40 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
             KillPath(p);
             return;
         }
+#pragma unroll
         for (int k = 0; k < kNLambda; ++k) p.beta[k] /= 1 - q;
     }
 }
 
-// RGBFilm::AddSample (film.h:241-258) with PixelSensor::ToSensorRGB (film.h:95-100).  Returns the
-// weighted sensor rgb and weight to add into the pixel.
-B2_HD void FinishPath(const RenderSceneDev &rs, PathRegs &p, bool lastOccluded, float rgbw[4]) {
-    if (p.flags & PF_SHADOW_PENDING) {
-        if (!lastOccluded)
-            for (int k = 0; k < kNLambda; ++k) p.L[k] += p.Ld[k];
-        p.flags &= ~PF_SHADOW_PENDING;
-    }
-    float lambda[kNLambda];
-    SampleWavelengths(p.lambdaU, lambda);
-    const float pdf = 1 / (kLambdaMax - kLambdaMin);
-    float rgb[3] = {0, 0, 0};
+// RGBFilm::AddSample (film.h:241-258) with PixelSensor::ToSensorRGB (film.h:95-100) on
+// L = SafeDiv(L, lambda.PDF()) (cpu/integrators.cpp:264-268).  L(k) reads the path's radiance.
+template <class LFn>
+B2_HD void FinishPath(const RenderSceneDev &rs, float lambdaU, uint32_t flags, float filterWeight, LFn L,
+                      float rgbw[4]) {
+    const float pdfU = 1 / (kLambdaMax - kLambdaMin);
+    bool term = (flags & PF_TERMINATED_SECONDARY) != 0;
     bool bad = false;
-    for (int k = 0; k < kNLambda; ++k) bad |= std::isnan(p.L[k]) | std::isinf(p.L[k]);
-    for (int c = 0; c < 3; ++c) {
-        const SpectrumTable &bar = rs.spectra[rs.film.sensorSpectrum[c]];
-        float sum = 0;
-        for (int k = 0; k < kNLambda; ++k) {
-            float Lk = bad ? 0.f : p.L[k] / pdf;  // SafeDiv(L, lambda.PDF())
-            sum += SpectrumAt(bar, lambda[k]) * Lk;
-        }
-        rgb[c] = rs.film.imagingRatio * (sum / kNLambda);
+#pragma unroll
+    for (int k = 0; k < kNLambda; ++k) {
+        float v = L(k);
+        bad |= std::isnan(v) | std::isinf(v);
     }
+    const SpectrumTable &rb = rs.spectra[rs.film.sensorSpectrum[0]];
+    const SpectrumTable &gb = rs.spectra[rs.film.sensorSpectrum[1]];
+    const SpectrumTable &bb = rs.spectra[rs.film.sensorSpectrum[2]];
+    float sum[3] = {0, 0, 0};
+    LambdaIter li(lambdaU);
+#pragma unroll
+    for (int k = 0; k < kNLambda; ++k, li.Next()) {
+        // after TerminateSecondary: pdf[0] = pdfU / 31, pdf[k > 0] = 0 (SafeDiv gives 0)
+        float pdf = term ? (k == 0 ? pdfU / kNLambda : 0.f) : pdfU;
+        float Lk = (bad || pdf == 0) ? 0.f : L(k) / pdf;
+        sum[0] += SpectrumAt(rb, li.lam) * Lk;
+        sum[1] += SpectrumAt(gb, li.lam) * Lk;
+        sum[2] += SpectrumAt(bb, li.lam) * Lk;
+    }
+    float rgb[3];
+    for (int c = 0; c < 3; ++c) rgb[c] = rs.film.imagingRatio * (sum[c] / kNLambda);
     float m = fmaxf(rgb[0], fmaxf(rgb[1], rgb[2]));
     if (m > rs.film.maxComponentValue) {
         float sc = rs.film.maxComponentValue / m;
@@ -281,10 +384,10 @@ B2_HD void FinishPath(const RenderSceneDev &rs, PathRegs &p, bool lastOccluded, 
         rgb[1] *= sc;
         rgb[2] *= sc;
     }
-    rgbw[0] = p.filterWeight * rgb[0];
-    rgbw[1] = p.filterWeight * rgb[1];
-    rgbw[2] = p.filterWeight * rgb[2];
-    rgbw[3] = p.filterWeight;
+    rgbw[0] = filterWeight * rgb[0];
+    rgbw[1] = filterWeight * rgb[1];
+    rgbw[2] = filterWeight * rgb[2];
+    rgbw[3] = filterWeight;
 }
 
 }  // namespace b200pt

@@ -59,7 +59,7 @@ B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b
     h.n = n;
     h.ns = n;
     h.dpdus = dpdu;
-    h.wo = wo;
+    h.wo = Normalize(wo);  // Interaction constructor (interaction.h:36-41)
     return h;
 }
 
@@ -71,9 +71,9 @@ struct LightCtx {  // LightSampleContext (lights.h:83-101)
 
 // DiffuseAreaLight::L (lights.h:444-470) without image / alpha.
 B2_HD bool AreaLightEmits(const LightDev &l, V3 n, V3 w) {
-    if (!l.twoSided && Dot(n, w) < 0) return false;
+    if (!l.twoSided && DotN(n, w) < 0) return false;
     if (l.cosFalloffEnd > 0) {
-        float cosTheta = AbsDot(w, n);
+        float cosTheta = AbsDotN(n, w);
         if (cosTheta < l.cosFalloffEnd) return false;
     }
     return true;
@@ -196,10 +196,10 @@ constexpr float kMaxSphericalSampleArea = 6.22f;
 
 B2_HD void CosWarpWeights(const TriVerts &t, V3 rp, V3 ns, float w[4]) {  // shapes.h:1081-1087
     V3 wi0 = Normalize(t.p0 - rp), wi1 = Normalize(t.p1 - rp), wi2 = Normalize(t.p2 - rp);
-    w[0] = fmaxf(0.01f, AbsDot(ns, wi1));
-    w[1] = fmaxf(0.01f, AbsDot(ns, wi1));
-    w[2] = fmaxf(0.01f, AbsDot(ns, wi0));
-    w[3] = fmaxf(0.01f, AbsDot(ns, wi2));
+    w[0] = fmaxf(0.01f, AbsDotN(ns, wi1));
+    w[1] = fmaxf(0.01f, AbsDotN(ns, wi1));
+    w[2] = fmaxf(0.01f, AbsDotN(ns, wi0));
+    w[3] = fmaxf(0.01f, AbsDotN(ns, wi2));
 }
 
 // Triangle::Sample(ctx, u) (shapes.h:1052-1130)
@@ -217,7 +217,7 @@ B2_HD ShapeSampleOut SampleTriangleSolidAngle(const TriVerts &t, const LightCtx 
             return o;
         }
         wi = Normalize(wi);
-        o.pdf /= AbsDot(o.n, -wi) / LengthSquared(rp - Mid(o.pi));
+        o.pdf /= AbsDotN(o.n, -wi) / LengthSquared(rp - Mid(o.pi));
         if (std::isinf(o.pdf)) o.ok = false;
         return o;
     }
@@ -263,7 +263,7 @@ B2_HD float TrianglePDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flip
         V3 pHit = b0 * t.p0 + b1 * t.p1 + b2 * t.p2;
         V3 pAbsSum = Abs(b0 * t.p0) + Abs(b1 * t.p1) + Abs(b2 * t.p2);
         P3i pi = MakeP3i(pHit, GammaF(7) * pAbsSum);
-        float pdf = (1 / TriArea(t)) / (AbsDot(n, -wi) / LengthSquared(rp - Mid(pi)));
+        float pdf = (1 / TriArea(t)) / (AbsDotN(n, -wi) / LengthSquared(rp - Mid(pi)));
         if (std::isinf(pdf)) pdf = 0;
         return pdf;
     }

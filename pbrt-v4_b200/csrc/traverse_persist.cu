@@ -58,7 +58,9 @@ template <bool ANY, bool COUNT, bool INTERNAL>
 __global__ void __launch_bounds__(kBlock)
 TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200pt_hit *__restrict__ hits,
                       unsigned char *__restrict__ occluded, int *__restrict__ rayCounter,
-                      unsigned long long *__restrict__ counters, int kRefillMin, int kNodeMin) {
+                      unsigned long long *__restrict__ counters, int kRefillMin, int kNodeMin,
+                      const int *__restrict__ nDev) {
+    if (nDev) n = min(n, *nDev);  // queue length written by an earlier kernel of the stream
     __shared__ int2 smemStack[kSmemDepth * kBlock];
     int2 *stack = smemStack + threadIdx.x;  // entry d lives at stack[d * kBlock]
     int2 deep[kLocalDepth];
@@ -232,7 +234,8 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
 cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long long n, b200pt_hit *hits,
                                   unsigned char *occluded, bool any, int *rayCounter,
                                   unsigned long long *counters, int smCount, int stackDepth,
-                                  int refillMin, int nodeMin, cudaStream_t stream, bool internalHits) {
+                                  int refillMin, int nodeMin, cudaStream_t stream, bool internalHits,
+                                  const int *nDev) {
     if (n <= 0) return cudaSuccess;
     if (n > 0x7fffffffll) return cudaErrorInvalidValue;
     if (stackDepth > kSmemDepth + kLocalDepth) return cudaErrorInvalidValue;
@@ -248,7 +251,7 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
         e = cudaMemsetAsync(rayCounter, 0, sizeof(int), stream);
         if (e != cudaSuccess) return e;
         kern<<<grid, kBlock, smemBytes, stream>>>(sc, rays, (int)n, hits, occluded, rayCounter, counters, refillMin,
-                                                  nodeMin);
+                                                  nodeMin, nDev);
         return cudaGetLastError();
     };
     if (any)

@@ -251,24 +251,42 @@ def _mesh_pbrt(m):
     return f'Shape "trianglemesh" "integer indices" [{idx}] "point3 P" [{pts}]'
 
 
-def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0):
+# Material lines for cornell_pbrt(boxes=...): the BxDF families of BASELINE.json configs[2]
+MATERIALS = {
+    "conductor_rough": 'Material "conductor" "spectrum eta" "metal-Cu-eta" "spectrum k" "metal-Cu-k" "float roughness" 0.05',
+    "conductor_smooth": 'Material "conductor" "spectrum eta" "metal-Au-eta" "spectrum k" "metal-Au-k" "float roughness" 0',
+    "conductor_reflectance": 'Material "conductor" "rgb reflectance" [0.8 0.6 0.3] "float uroughness" 0.2 "float vroughness" 0.05',
+    "dielectric_smooth": 'Material "dielectric" "float eta" 1.5',
+    "dielectric_rough": 'Material "dielectric" "float eta" 1.5 "float roughness" 0.1',
+    "dielectric_glass": 'Material "dielectric" "spectrum eta" "glass-BK7"',
+    "coated_diffuse": 'Material "coateddiffuse" "rgb reflectance" [0.2 0.3 0.7] "float roughness" 0',
+    "coated_diffuse_rough": 'Material "coateddiffuse" "rgb reflectance" [0.7 0.3 0.2] "float roughness" 0.1 "float thickness" 0.02',
+}
+
+
+def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
+                 boxes=(None, None), regularize=False):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     colours = [white, white, white, red, green, None, white, white]
+    override = {6: boxes[0], 7: boxes[1]}  # the short and the tall box
     lines = [
         'LookAt 0.5 0.5 -1.4  0.5 0.5 0.5  0 1 0',
         'Camera "perspective" "float fov" 39.3',
         f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
-        f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "{lightsampler}"',
+        f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "{lightsampler}"'
+        + (' "bool regularize" true' if regularize else ''),
         'PixelFilter "box"',
         f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false',
         'WorldBegin',
     ]
-    for m, c in zip(sc.meshes, colours):
+    for k, (m, c) in enumerate(zip(sc.meshes, colours)):
         lines.append('AttributeBegin')
-        if c is None:
+        if override.get(k):
+            lines.append('  ' + MATERIALS.get(override[k], override[k]))
+        elif c is None:
             lines.append('  AreaLightSource "diffuse" "rgb L" [17 12 4]')
             lines.append('  Material "diffuse" "rgb reflectance" [0 0 0]')
         else:

@@ -73,6 +73,23 @@ bool Trace(const HostScene &hs, V3 o, V3 d, float tMax, bool any, uint32_t hit[6
     return true;
 }
 
+// the IO of ShadeVertex on the host: plain arrays, shadow ray resolved right after the vertex
+struct HostIO {
+    float L[kNLambda], Ld[kNLambda];
+    bool shadow;
+    V3 shO, shD;
+    float shTMax;
+    void AddL(int k, float v) { L[k] += v; }
+    void ShadowBegin() {}
+    void SetLd(int k, float v) { Ld[k] = v; }
+    void ShadowEnd(bool valid, V3 o, V3 d, float tMax) {
+        shadow = valid;
+        shO = o;
+        shD = d;
+        shTMax = tMax;
+    }
+};
+
 }  // namespace
 
 // rgbw: 4 doubles per pixel (rgbSum, weightSum), row major.  Returns 0 or an error code; err text in msg.
@@ -103,22 +120,72 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
                     for (int k = 0; k < nSamples; ++k) {
                         PathRegs p;
                         GenerateCameraPath(rs, p, rs.film.x0 + x, rs.film.y0 + y, firstSample + k * stride);
-                        bool occluded = false;
+                        HostIO io;
+                        for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f;
                         // depth loop: one closest-hit + one shadow ray per vertex, as the kernels do
                         while (p.flags & PF_ALIVE) {
                             uint32_t hit[6] = {kMissTag, 0, 0, 0, 0, 0};
                             Trace(hs, p.rayO, p.rayD, p.rayTMax, false, hit);
-                            ShadeVertex(rs, p, hit, occluded);
-                            occluded = false;
-                            if (p.flags & PF_SHADOW_PENDING) occluded = Trace(hs, p.shO, p.shD, p.shTMax, true, nullptr);
+                            io.shadow = false;
+                            ShadeVertex(rs, p, hit, io);
+                            if (io.shadow && !Trace(hs, io.shO, io.shD, io.shTMax, true, nullptr))
+                                for (int i = 0; i < kNLambda; ++i) io.L[i] += io.Ld[i];
                         }
                         float out[4];
-                        FinishPath(rs, p, occluded, out);
+                        FinishPath(rs, p.lambdaU, p.flags, p.filterWeight, [&](int i) { return io.L[i]; }, out);
                         double *px = rgbw + 4 * (size_t(y) * W + x);
                         for (int c = 0; c < 4; ++c) px[c] += out[c];
                     }
         });
     for (auto &th : pool) th.join();
+    return 0;
+}
+
+// Debug twin of `dumpscene_ref scene.pbrt --path x y s`: radiance of one pixel sample with maxDepth cut
+// at 0, 1, 2, ... and the vertices visited.
+extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render_desc *rd, int x, int y, int si) {
+    HostScene hs;
+    RenderHost rh;
+    std::string err;
+    int rc = AssembleScene(sd, hs, err);
+    if (rc == 0) rc = BuildRenderTables(rd, hs, sd->n_meshes, rh, err);
+    if (rc != 0) return rc;
+    RenderSceneDev rs = rh.rs;
+    rs.spectra = rh.spectra.data();
+    rs.materials = rh.materials.data();
+    rs.lights = rh.lights.data();
+    rs.meshes = rh.meshes.data();
+    rs.prims = hs.prims.data();
+    int full = rs.integrator.maxDepth;
+    for (int d = 0; d <= full; ++d) {
+        rs.integrator.maxDepth = d;
+        PathRegs p;
+        GenerateCameraPath(rs, p, x, y, si);
+        HostIO io;
+        for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f;
+        V3 o = p.rayO, dd = p.rayD;
+        while (p.flags & PF_ALIVE) {
+            uint32_t hit[6] = {kMissTag, 0, 0, 0, 0, 0};
+            Trace(hs, p.rayO, p.rayD, p.rayTMax, false, hit);
+            if (d == full) {
+                float t;
+                memcpy(&t, &hit[1], 4);
+                const PrimSlot *ps = hit[0] == kMissTag ? nullptr : &hs.prims[hit[0]];
+                printf("   vertex depth %d: o %.9g %.9g %.9g d %.9g %.9g %.9g -> mesh %d tri %d t %.9g  beta0 %.9g dim %d\n",
+                       p.depth, p.rayO.x, p.rayO.y, p.rayO.z, p.rayD.x, p.rayD.y, p.rayD.z, ps ? int(ps->mesh) : -1,
+                       ps ? int(ps->tri) : -1, t, p.beta[0], p.dimension); printf("      etaScale %.9g beta0*etaScale %.9g\n", p.etaScale, p.beta[0]*p.etaScale);
+            }
+            io.shadow = false;
+            ShadeVertex(rs, p, hit, io);
+            bool occ = io.shadow && Trace(hs, io.shO, io.shD, io.shTMax, true, nullptr);
+            if (d == full && io.shadow) printf("      shadow ray occluded %d Ld0 %.9g\n", int(occ), io.Ld[0]);
+            if (io.shadow && !occ)
+                for (int i = 0; i < kNLambda; ++i) io.L[i] += io.Ld[i];
+        }
+        printf("maxdepth %d  lambda0 %.9g  o %.9g %.9g %.9g  d %.9g %.9g %.9g  L0 %.9g L1 %.9g L15 %.9g L30 %.9g\n", d,
+               LambdaIter(p.lambdaU).lam, o.x, o.y, o.z, dd.x, dd.y, dd.z, io.L[0], io.L[1], io.L[15], io.L[30]);
+    }
+    fflush(stdout);
     return 0;
 }
 
