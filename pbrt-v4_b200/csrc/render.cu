@@ -118,7 +118,11 @@ struct DevIO {
     int path;
     int *nShadow;
     int slot;
-    __device__ DevIO(const PassBuffers &b, int pathId, int *shadowCount) : pb(b), path(pathId), nShadow(shadowCount), slot(-1) {}
+    float *beta;  // this thread's column of the block's [31][kShadeBlock] shared array
+    __device__ DevIO(const PassBuffers &b, int pathId, int *shadowCount, float *sbeta)
+        : pb(b), path(pathId), nShadow(shadowCount), slot(-1), beta(sbeta) {}
+    __device__ __forceinline__ float Beta(int k) const { return beta[k * kShadeBlock]; }
+    __device__ __forceinline__ void SetBeta(int k, float v) { beta[k * kShadeBlock] = v; }
     __device__ __forceinline__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
     __device__ __forceinline__ void ShadowBegin() { slot = QueuePush(nShadow); }
     __device__ __forceinline__ void SetLd(int k, float v) { pb.Ld[(long long)k * pb.n + slot] = v; }
@@ -177,10 +181,13 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     int q = pb.matQ[MAT][t];
     int path = pb.rayPath[cur][q];
     const long long n = pb.n;
+    // throughput in shared memory, [k][thread]: indexable by k without costing registers or local memory
+    __shared__ float sbeta[kNLambda * kShadeBlock];
+    float *myBeta = sbeta + threadIdx.x;
     PathRegs p;
     LoadHeader(pb, path, p);
-#pragma unroll
-    for (int k = 0; k < kNLambda; ++k) p.beta[k] = pb.beta[k * n + path];
+#pragma unroll 8
+    for (int k = 0; k < kNLambda; ++k) myBeta[k * kShadeBlock] = pb.beta[k * n + path];
     int pix = path % nPixels;
     p.px = rs.film.x0 + pix % width;
     p.py = rs.film.y0 + pix / width;
@@ -192,15 +199,15 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     const uint2 *h = reinterpret_cast<const uint2 *>(pb.hits + 6ll * q);
     uint2 h0 = h[0], h1 = h[1], h2 = h[2];
     hit[0] = h0.x; hit[1] = h0.y; hit[2] = h1.x; hit[3] = h1.y; hit[4] = h2.x; hit[5] = h2.y;
-    DevIO io(pb, path, counts + 1);
+    DevIO io(pb, path, counts + 1, myBeta);
     ShadeVertex<DevIO, MAT>(rs, p, hit, io);
     if (p.flags & PF_ALIVE) {
         int *next = pb.counts + kCountStride * (depth + 1);
         int slot = QueuePush(next);
         StoreRay(pb.rays[nxt], slot, p.rayO, p.rayD, p.rayTMax);
         pb.rayPath[nxt][slot] = path;
-#pragma unroll
-        for (int k = 0; k < kNLambda; ++k) pb.beta[k * n + path] = p.beta[k];
+#pragma unroll 8
+        for (int k = 0; k < kNLambda; ++k) pb.beta[k * n + path] = myBeta[k * kShadeBlock];
         StoreHeader(pb, path, p);
     } else {
         pb.ints[3 * n + path] = (int)p.flags;  // the finish kernel needs PF_TERMINATED_SECONDARY

@@ -8,8 +8,10 @@
 //
 // Spectral work is written as streams over k = 0..30 with the wavelength carried along a
 // recurrence (LambdaIter), never as arrays of 31 that must stay live across the whole step: only
-// beta[31] lives in registers; L and the pending Ld are reached through the IO object (global
-// memory on the device, plain arrays in tests/native/rendercheck.cpp).
+// beta, L and the pending Ld are reached through the IO object (beta in shared memory and L / Ld in
+// global memory on the device, plain arrays in tests/native/rendercheck.cpp).  The loops are kept
+// rolled (B2_SPECTRAL_LOOP): fully unrolled, the 31 copies of every loop body made the shading
+// kernel ~20 K instructions and instruction-fetch bound (profiles/r01_render_v2_*).
 #pragma once
 #include "render_bsdf.h"
 
@@ -20,8 +22,13 @@ enum : uint32_t {
     PF_TERMINATED_SECONDARY = 16u  // SampledWavelengths::TerminateSecondary happened (util/spectrum.h:346-353)
 };
 
+#if defined(__CUDA_ARCH__)
+#define B2_SPECTRAL_LOOP _Pragma("unroll 2")
+#else
+#define B2_SPECTRAL_LOOP
+#endif
+
 struct PathRegs {
-    float beta[kNLambda];
     float lambdaU;
     int px, py, sampleIndex, dimension, depth;
     uint32_t flags;
@@ -68,8 +75,6 @@ B2_HD void GenerateCameraPath(const RenderSceneDev &rs, PathRegs &p, int px, int
     p.dimension = s.dimension;
     GeneratePerspectiveRay(rs.camera, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
     p.rayTMax = INFINITY;
-#pragma unroll
-    for (int k = 0; k < kNLambda; ++k) p.beta[k] = 1.f;
     p.depth = 0;
     p.flags = PF_ALIVE;
     p.etaScale = 1.f;
@@ -144,7 +149,8 @@ B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval
 
 // One path vertex.  `hit` is the internal record {slot, t, b0, b1, b2} of the closest-hit kernel for
 // p.ray.  IO: AddL(k, v) adds to the path's radiance; ShadowBegin() / SetLd(k, v) / ShadowEnd(valid,
-// o, d, tMax) record a light sample whose visibility is still unknown.
+// o, d, tMax) record a light sample whose visibility is still unknown; Beta(k) / SetBeta(k, v) are the
+// path throughput.
 template <class IO, int MAT = -1>
 B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit[6], IO &io) {
     if (hit[0] == kMissTag) {  // no infinite lights yet: an escaped ray adds nothing (cpu/integrators.cpp:645-662)
@@ -174,10 +180,10 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
             }
             const SpectrumTable &sp = rs.spectra[al.spectrum];
             LambdaIter li(p.lambdaU);
-#pragma unroll
+B2_SPECTRAL_LOOP
             for (int k = 0; k < kNLambda; ++k, li.Next()) {
                 float Le = al.scale * SpectrumAt(sp, li.lam);
-                if (Le != 0) io.AddL(k, p.beta[k] * w * Le);
+                if (Le != 0) io.AddL(k, io.Beta(k) * w * Le);
             }
         }
     }
@@ -193,7 +199,7 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
     if (bsdf.type == MAT_DIFFUSE) {  // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
         bool anyR = false;
         LambdaIter li(p.lambdaU);
-#pragma unroll
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k, li.Next()) anyR |= Clampf(SpectrumAt(rs.spectra[bsdf.specA], li.lam), 0, 1) != 0;
         if (!anyR) bflags = 0;
     }
@@ -263,11 +269,11 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
                         bool anyL = false, anyF = false;
                         io.ShadowBegin();
                         LambdaIter li(p.lambdaU);
-#pragma unroll
+B2_SPECTRAL_LOOP
                         for (int k = 0; k < kNLambda; ++k, li.Next()) {
                             float Le = light.scale * SpectrumAt(sp, li.lam) * atten;
                             float f = BsdfSpectral(rs, bsdf, ev, li.lam) * absCos;
-                            io.SetLd(k, p.beta[k] * (w_l * Le * f / p_l));
+                            io.SetLd(k, io.Beta(k) * (w_l * Le * f / p_l));
                             anyL |= Le != 0;
                             anyF |= f != 0;
                         }
@@ -305,11 +311,11 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
     bool anyF = false;
     {
         LambdaIter li(p.lambdaU);
-#pragma unroll
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k, li.Next()) {
             float f = BsdfSpectral(rs, bsdf, ev, li.lam);
             anyF |= f != 0;
-            p.beta[k] *= f * absCos / bs.pdf;
+            io.SetBeta(k, io.Beta(k) * (f * absCos / bs.pdf));
         }
     }
     if (!anyF) {  // !bs->f
@@ -328,9 +334,9 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
     p.rayTMax = INFINITY;
 
     // ---- Russian roulette (cpu/integrators.cpp:748-756)
-    float maxComp = p.beta[0] * p.etaScale;
-#pragma unroll
-    for (int k = 1; k < kNLambda; ++k) maxComp = fmaxf(maxComp, p.beta[k] * p.etaScale);
+    float maxComp = io.Beta(0) * p.etaScale;
+B2_SPECTRAL_LOOP
+    for (int k = 1; k < kNLambda; ++k) maxComp = fmaxf(maxComp, io.Beta(k) * p.etaScale);
 #ifdef B2_PATH_DEBUG
     printf("      rr maxComp %.9g\n", maxComp);
 #endif
@@ -343,8 +349,8 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
             KillPath(p);
             return;
         }
-#pragma unroll
-        for (int k = 0; k < kNLambda; ++k) p.beta[k] /= 1 - q;
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k) io.SetBeta(k, io.Beta(k) / (1 - q));
     }
 }
 
@@ -356,7 +362,7 @@ B2_HD void FinishPath(const RenderSceneDev &rs, float lambdaU, uint32_t flags, f
     const float pdfU = 1 / (kLambdaMax - kLambdaMin);
     bool term = (flags & PF_TERMINATED_SECONDARY) != 0;
     bool bad = false;
-#pragma unroll
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) {
         float v = L(k);
         bad |= std::isnan(v) | std::isinf(v);
@@ -366,7 +372,7 @@ B2_HD void FinishPath(const RenderSceneDev &rs, float lambdaU, uint32_t flags, f
     const SpectrumTable &bb = rs.spectra[rs.film.sensorSpectrum[2]];
     float sum[3] = {0, 0, 0};
     LambdaIter li(lambdaU);
-#pragma unroll
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k, li.Next()) {
         // after TerminateSecondary: pdf[0] = pdfU / 31, pdf[k > 0] = 0 (SafeDiv gives 0)
         float pdf = term ? (k == 0 ? pdfU / kNLambda : 0.f) : pdfU;

@@ -59,7 +59,9 @@ RENDER_CASES = {
 # that is 1 up to rounding, so a last-bit difference in a spectrum lookup decides whether one more
 # sampler dimension is consumed; such paths stay valid samples but stop following the reference's.
 # For these a second reference image at seed + 1 is stored (<name>_ref2.npy).
-NOISE_GATED = {"cornell_glass_r64_s16"}
+# (metal2 follows the reference path for path on the CPU check, which shares glibc's sinf/cosf with the
+# reference; on the GPU the last-bit differences of CUDA's sinf/cosf flip a few such roulette tests.)
+NOISE_GATED = {"cornell_glass_r64_s16", "cornell_metal2_r48_s8"}
 # scene tables only (no image): BASELINE.json configs[0] at full size, for bench.py and the
 # full-size GPU test, which render the reference image on the spot with oracle/_ref/pbrt_ref
 TABLE_CASES = {

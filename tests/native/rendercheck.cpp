@@ -75,10 +75,12 @@ bool Trace(const HostScene &hs, V3 o, V3 d, float tMax, bool any, uint32_t hit[6
 
 // the IO of ShadeVertex on the host: plain arrays, shadow ray resolved right after the vertex
 struct HostIO {
-    float L[kNLambda], Ld[kNLambda];
+    float L[kNLambda], Ld[kNLambda], beta[kNLambda];
     bool shadow;
     V3 shO, shD;
     float shTMax;
+    float Beta(int k) const { return beta[k]; }
+    void SetBeta(int k, float v) { beta[k] = v; }
     void AddL(int k, float v) { L[k] += v; }
     void ShadowBegin() {}
     void SetLd(int k, float v) { Ld[k] = v; }
@@ -121,7 +123,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
                         PathRegs p;
                         GenerateCameraPath(rs, p, rs.film.x0 + x, rs.film.y0 + y, firstSample + k * stride);
                         HostIO io;
-                        for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f;
+                        for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f, io.beta[i] = 1.f;
                         // depth loop: one closest-hit + one shadow ray per vertex, as the kernels do
                         while (p.flags & PF_ALIVE) {
                             uint32_t hit[6] = {kMissTag, 0, 0, 0, 0, 0};
@@ -162,7 +164,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
         PathRegs p;
         GenerateCameraPath(rs, p, x, y, si);
         HostIO io;
-        for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f;
+        for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f, io.beta[i] = 1.f;
         V3 o = p.rayO, dd = p.rayD;
         while (p.flags & PF_ALIVE) {
             uint32_t hit[6] = {kMissTag, 0, 0, 0, 0, 0};
@@ -173,7 +175,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
                 const PrimSlot *ps = hit[0] == kMissTag ? nullptr : &hs.prims[hit[0]];
                 printf("   vertex depth %d: o %.9g %.9g %.9g d %.9g %.9g %.9g -> mesh %d tri %d t %.9g  beta0 %.9g dim %d\n",
                        p.depth, p.rayO.x, p.rayO.y, p.rayO.z, p.rayD.x, p.rayD.y, p.rayD.z, ps ? int(ps->mesh) : -1,
-                       ps ? int(ps->tri) : -1, t, p.beta[0], p.dimension); printf("      etaScale %.9g beta0*etaScale %.9g\n", p.etaScale, p.beta[0]*p.etaScale);
+                       ps ? int(ps->tri) : -1, t, io.beta[0], p.dimension); printf("      etaScale %.9g beta0*etaScale %.9g\n", p.etaScale, io.beta[0]*p.etaScale);
             }
             io.shadow = false;
             ShadeVertex(rs, p, hit, io);
