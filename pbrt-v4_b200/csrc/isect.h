@@ -17,6 +17,7 @@
 
 #if defined(__CUDA_ARCH__)
 #define B2_HD __host__ __device__ __forceinline__
+#define B2_HD_NOINLINE __host__ __device__ __noinline__
 #define B2_MUL(a, b) __fmul_rn((a), (b))
 #define B2_ADD(a, b) __fadd_rn((a), (b))
 #define B2_SUB(a, b) __fsub_rn((a), (b))
@@ -28,8 +29,10 @@
 #else
 #if defined(__CUDACC__)
 #define B2_HD __host__ __device__ inline
+#define B2_HD_NOINLINE __host__ __device__ inline
 #else
 #define B2_HD inline
+#define B2_HD_NOINLINE inline
 #endif
 #define B2_MUL(a, b) ((a) * (b))
 #define B2_ADD(a, b) ((a) + (b))

@@ -125,13 +125,15 @@ B2_HD float SobolSampleZ(uint64_t a, int dim, uint32_t randomize, uint32_t hash)
     else if (randomize == 3) v = OwenScramble(v, hash);
     return fminf(v * 0x1p-32f, kOneMinusEps);
 }
-B2_HD float ZSobolGet1D(ZSobol &s) {  // samplers.h:258-272
+// (not inlined on the device: the shading kernels call these five or six times per vertex and the
+// code would otherwise be replicated at every call site)
+B2_HD_NOINLINE float ZSobolGet1D(ZSobol &s) {  // samplers.h:258-272
     uint64_t idx = ZSobolSampleIndex(s);
     ++s.dimension;
     uint32_t h = (uint32_t)Hash2i(s.dimension, s.seed);
     return SobolSampleZ(idx, 0, s.randomize, h);
 }
-B2_HD void ZSobolGet2D(ZSobol &s, float &u0, float &u1) {  // samplers.h:274-293
+B2_HD_NOINLINE void ZSobolGet2D(ZSobol &s, float &u0, float &u1) {  // samplers.h:274-293
     uint64_t idx = ZSobolSampleIndex(s);
     s.dimension += 2;
     uint64_t bits = Hash2i(s.dimension, s.seed);

@@ -115,7 +115,7 @@ B2_HD V3 Mid(const P3i &p) { return mk((p.lo.x + p.hi.x) / 2, (p.lo.y + p.hi.y) 
 B2_HD V3 Err(const P3i &p) { return mk((p.hi.x - p.lo.x) / 2, (p.hi.y - p.lo.y) / 2, (p.hi.z - p.lo.z) / 2); }
 
 // OffsetRayOrigin (ray.h:78-95)
-B2_HD V3 OffsetRayOrigin(const P3i &pi, V3 n, V3 w) {
+B2_HD_NOINLINE V3 OffsetRayOrigin(const P3i &pi, V3 n, V3 w) {
     float d = DotN(Abs(n), Err(pi));
     V3 offset = d * n;
     if (DotN(n, w) < 0) offset = -offset;
