@@ -140,6 +140,10 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
         e = cudaMemcpyAsync(s->dPairs, h.pairs.data(), h.pairs.size() * sizeof(PairNode), cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(s->dNodes, h.nodes.data(), nodeBytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(s->dPrims, h.prims.data(), primBytes, cudaMemcpyHostToDevice, ctx->stream);
+    size_t instBytes = h.instances.size() * sizeof(InstanceDev);
+    if (e == cudaSuccess && instBytes) e = cudaMalloc(&s->dInst, instBytes);
+    if (e == cudaSuccess && instBytes)
+        e = cudaMemcpyAsync(s->dInst, h.instances.data(), instBytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) {
         ctx->err = std::string("scene upload: ") + cudaGetErrorString(e);
@@ -151,17 +155,17 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     s->dev.pairs = s->dPairs;
     std::memcpy(s->dev.rootBox, h.bounds, 24);
     s->dev.rootRef = h.rootRef;
-    s->dev.instances = nullptr;
+    s->dev.instances = (const InstanceDev *)s->dInst;
     s->dev.rootNode = h.rootNode;
     s->dev.nNodes = uint32_t(h.nodes.size());
     s->dev.nPrims = uint32_t(h.prims.size());
-    s->dev.nInstances = 0;
+    s->dev.nInstances = uint32_t(h.instances.size());
     s->dev.maxDepth = h.maxDepth;
     s->stats.n_triangles = h.nTriangles;
-    s->stats.n_instances = 0;
+    s->stats.n_instances = h.instances.size();
     s->stats.n_bvh2_nodes = h.nodes.size();
     s->stats.n_wide_nodes = h.pairs.size();
-    s->stats.device_bytes = nodeBytes + primBytes + pairBytes;
+    s->stats.device_bytes = nodeBytes + primBytes + pairBytes + instBytes;
     s->stats.build_seconds = h.buildSeconds;
     s->stats.upload_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     *out = s;
@@ -235,6 +239,10 @@ static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, u
     }
     if (count) B2_CUDA(ctx, cudaMemsetAsync(ctx->dCounters, 0, 8 * sizeof(unsigned long long), ctx->stream));
     B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    if (ctx->simpleKernel && s->dev.nInstances) {
+        ctx->err = "B200PT_TRAVERSAL=simple (the parity kernel) does not handle object instances";
+        return B200PT_ERR_INVALID;
+    }
     if (ctx->simpleKernel)
         B2_CUDA(ctx, LaunchTraverseBVH2(s->dev, dRays, n, any ? nullptr : (b200pt_hit *)dOut,
                                         any ? (unsigned char *)dOut : nullptr, any,

@@ -41,12 +41,17 @@ static_assert(sizeof(PairNode) == 64, "PairNode is two 32-byte loads");
 
 // One entry per object instance (TransformedPrimitive, cpu/primitive.cpp:112-131).
 struct alignas(16) InstanceDev {
-    float m[12];     // renderFromInstance rows 0..2
-    float mInv[12];  // its inverse, rows 0..2
-    uint32_t rootNode;   // root of the object's tree in `nodes`
+    float mInv[12];      // instanceFromRender rows 0..2 (the ray goes through this: instance.h)
+    float m[12];         // renderFromInstance rows 0..2 (the hit comes back through this)
+    float rootBox[6];    // bounds of the object's BVH root, object space
+    int32_t rootRef;     // PairNode index of the object's root, or ~slot when the object is one primitive
+                         // (then there is no BVH and no box test: scene.cpp:1542-1551)
     uint32_t instanceId; // 1-based (scene.cpp:1560)
+    uint32_t rootNode;   // the same root in `nodes` (Node32 layout)
+    uint32_t object;
     uint32_t pad[2];
 };
+static_assert(sizeof(InstanceDev) == 144, "InstanceDev layout");
 
 struct DeviceScene {
     const void *nodes;   // Node32[], 32 B, child/prim offsets absolute (parity kernel)

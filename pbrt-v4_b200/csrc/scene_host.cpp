@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstring>
+#include <limits>
 #include <map>
 
 namespace b200pt {
@@ -86,9 +87,17 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
     }
     out.nTriangles = nTri;
     out.nMeshes = desc->n_meshes;
-    if (desc->n_instances) {
-        err = "instances are not supported by this build yet";
-        return B200PT_ERR_INVALID;
+    for (uint32_t i = 0; i < desc->n_instances; ++i) {
+        const b200pt_instance &in = desc->instances[i];
+        const float *r3 = in.instance_from_render + 12, *f3 = in.render_from_instance + 12;
+        if (r3[0] != 0 || r3[1] != 0 || r3[2] != 0 || r3[3] != 1 || f3[0] != 0 || f3[1] != 0 || f3[2] != 0 || f3[3] != 1) {
+            err = "instance transforms must be affine (last row 0 0 0 1)";
+            return B200PT_ERR_INVALID;
+        }
+        if (!objMeshes.count(int32_t(in.object)) || int32_t(in.object) < 0) {
+            err = "instance of an undefined object";
+            return B200PT_ERR_INVALID;
+        }
     }
     if (nTri == 0) {
         err = "scene has no primitives";
@@ -124,11 +133,42 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
         // primitive order = the order the reference creates them in: meshes in
         // array order, triangles in index order (shapes.cpp:284-289), world
         // shapes before instances (scene.cpp:1447-1580).
+        // object definitions: one BVH each with maxPrimsInNode 1 (scene.cpp:1542 -> BVHAggregate's
+        // default); an object of a single primitive gets a one-leaf tree, which the traversal enters
+        // without a box test (the reference holds that primitive directly, scene.cpp:1551).
+        std::vector<HostTree> objTrees;
+        std::map<int32_t, Box> objBounds;
         for (auto &kv : objMeshes) {
             if (kv.first == -1)
                 continue;
-            err = "object definitions are not supported by this build yet";
-            return B200PT_ERR_INVALID;
+            HostTree t;
+            t.object = kv.first;
+            std::vector<Box> ob;
+            std::vector<PrimRef> orf;
+            for (uint32_t m : kv.second) {
+                const b200pt_mesh &mesh = desc->meshes[m];
+                for (uint32_t i = 0; i < mesh.n_triangles; ++i) {
+                    const int32_t *v = mesh.indices + 3ull * i;
+                    ob.push_back(TriBox(mesh.p + 3ull * v[0], mesh.p + 3ull * v[1], mesh.p + 3ull * v[2]));
+                    orf.push_back({0, m, i});
+                }
+            }
+            if (ob.empty()) {
+                err = "object definition without triangles";
+                return B200PT_ERR_INVALID;
+            }
+            std::vector<uint32_t> oorder;
+            BuildBVH2(ob.data(), uint32_t(ob.size()), 1, t.nodes, oorder);
+            for (uint32_t id : oorder) {
+                t.prims.push_back(orf[id].kind);
+                t.prims.push_back(orf[id].a);
+                t.prims.push_back(orf[id].b);
+            }
+            Box bb;
+            std::memcpy(bb.lo, t.nodes[0].bmin, 12);
+            std::memcpy(bb.hi, t.nodes[0].bmax, 12);
+            objBounds[kv.first] = bb;
+            objTrees.push_back(std::move(t));
         }
         HostTree top;
         top.object = -1;
@@ -142,6 +182,30 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                 refs.push_back({0, m, i});
             }
         }
+        for (uint32_t i = 0; i < desc->n_instances; ++i) {
+            // TransformedPrimitive::Bounds = renderFromPrimitive(primitive.Bounds()): union of the 8
+            // transformed corners (util/transform.cpp:134-139, util/transform.h:310-319)
+            const b200pt_instance &in = desc->instances[i];
+            const Box &ob = objBounds[int32_t(in.object)];
+            const float *m = in.render_from_instance;
+            Box bb;
+            for (int c = 0; c < 3; ++c) {
+                bb.lo[c] = std::numeric_limits<float>::max();
+                bb.hi[c] = std::numeric_limits<float>::lowest();
+            }
+            for (int corner = 0; corner < 8; ++corner) {
+                float x = (corner & 1) ? ob.hi[0] : ob.lo[0], y = (corner & 2) ? ob.hi[1] : ob.lo[1],
+                      z = (corner & 4) ? ob.hi[2] : ob.lo[2];
+                float pt[3];
+                for (int r = 0; r < 3; ++r) pt[r] = m[4 * r] * x + m[4 * r + 1] * y + m[4 * r + 2] * z + m[4 * r + 3];
+                for (int c = 0; c < 3; ++c) {
+                    bb.lo[c] = std::min(bb.lo[c], pt[c]);
+                    bb.hi[c] = std::max(bb.hi[c], pt[c]);
+                }
+            }
+            boxes.push_back(bb);
+            refs.push_back({1, i + 1, 0});
+        }
         std::vector<uint32_t> order;
         BuildBVH2(boxes.data(), uint32_t(boxes.size()), 4, top.nodes, order);
         top.prims.reserve(3 * order.size());
@@ -151,6 +215,7 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             top.prims.push_back(refs[id].b);
         }
         out.trees.push_back(std::move(top));
+        for (HostTree &t : objTrees) out.trees.push_back(std::move(t));
     }
 
     // ---- flatten all trees into one node array + depth-first primitive slots
@@ -184,8 +249,15 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                         std::memcpy(s.p2, mesh.p + 3ull * v[2], 12);
                         s.mesh = pr[1];
                         s.tri = pr[2];
+                    } else if (pr[0] == 1 && t.object == -1) {
+                        if (pr[1] < 1 || pr[1] > desc->n_instances) {
+                            err = "bvh primitive refers to a missing instance";
+                            return B200PT_ERR_INVALID;
+                        }
+                        s.mesh = kInstanceTag;
+                        s.tri = pr[1] - 1;  // index into the instance table
                     } else {
-                        err = "instance primitives are not supported by this build yet";
+                        err = "bad bvh primitive kind (instances only at the top level)";
                         return B200PT_ERR_INVALID;
                     }
                     out.prims.push_back(s);
@@ -194,6 +266,10 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             }
             out.nodes.push_back(nd);
         }
+    }
+    if (out.prims.size() >= (1ull << 30)) {
+        err = "too many primitive slots (2^30 limit of the traversal stack encoding)";
+        return B200PT_ERR_INVALID;
     }
     // ---- production layout: interior nodes only, children's boxes in the parent
     out.pairs.clear();
@@ -227,14 +303,41 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             out.treeRootRef.push_back(refOf[r]);
         out.rootRef = out.treeRootRef[0];
     }
+    // ---- instance table
+    out.instances.clear();
+    {
+        std::map<int32_t, size_t> treeOfObject;
+        for (size_t ti = 1; ti < out.trees.size(); ++ti) treeOfObject[out.trees[ti].object] = ti;
+        for (uint32_t i = 0; i < desc->n_instances; ++i) {
+            const b200pt_instance &in = desc->instances[i];
+            auto it = treeOfObject.find(int32_t(in.object));
+            if (it == treeOfObject.end()) {
+                err = "no bvh given for an instanced object";
+                return B200PT_ERR_INVALID;
+            }
+            InstanceDev d;
+            std::memset(&d, 0, sizeof d);
+            std::memcpy(d.mInv, in.instance_from_render, 48);
+            std::memcpy(d.m, in.render_from_instance, 48);
+            const Node32 &root = out.nodes[out.treeRoot[it->second]];
+            std::memcpy(d.rootBox, root.bmin, 12);
+            std::memcpy(d.rootBox + 3, root.bmax, 12);
+            d.rootRef = out.treeRootRef[it->second];
+            d.rootNode = out.treeRoot[it->second];
+            d.instanceId = i + 1;
+            d.object = in.object;
+            out.instances.push_back(d);
+        }
+    }
     // deepest root-to-leaf path (sizes the traversal stack; the reference's is a fixed 64)
     out.maxDepth = 1;
+    uint32_t topDepth = 1, objDepth = 0;
     for (size_t ti = 0; ti < out.trees.size(); ++ti) {
         std::vector<std::pair<uint32_t, uint32_t>> st{{out.treeRoot[ti], 1u}};
         while (!st.empty()) {
             auto [i, d] = st.back();
             st.pop_back();
-            out.maxDepth = std::max(out.maxDepth, d);
+            (ti == 0 ? topDepth : objDepth) = std::max(ti == 0 ? topDepth : objDepth, d);
             const Node32 &nd = out.nodes[i];
             if (nd.nPrims == 0) {
                 st.push_back({i + 1, d + 1});
@@ -242,6 +345,9 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             }
         }
     }
+    // an instance is entered from a top-level leaf: its entries sit on top of the parent's, plus the two
+    // entries that hold the way back (traverse_persist.cu)
+    out.maxDepth = topDepth + (objDepth ? objDepth + 2 : 0);
     out.rootNode = out.treeRoot[0];
     const Node32 &root = out.nodes[out.rootNode];
     std::memcpy(out.bounds, root.bmin, 12);

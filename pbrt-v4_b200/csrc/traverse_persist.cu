@@ -16,6 +16,7 @@
 
 #include "bvh2.h"
 #include "device_scene.h"
+#include "instance.h"
 #include "isect.h"
 #include "kernels.h"
 #include "../../include/b200pt.h"
@@ -52,9 +53,16 @@ enum : int { S_IDLE = 0, S_NODE = 1, S_LEAF = 2, S_DONE = 3 };
 constexpr int kSmemDepth = 24;
 constexpr int kLocalDepth = 72;
 
-// INTERNAL: closest-hit records for the shading kernels {slot, t, b0, b1, b2, 0} instead of the
-// public b200pt_hit (the PrimSlot index saves the shader the (mesh, tri) -> vertices lookup).
-template <bool ANY, bool COUNT, bool INTERNAL>
+// INTERNAL: closest-hit records for the shading kernels {slot, t, b0, b1, b2, instance + 1} instead of
+// the public b200pt_hit (the PrimSlot index saves the shader the (mesh, tri) -> vertices lookup).
+// INST: the scene has object instances (TransformedPrimitive, cpu/primitive.cpp:112-131).  A leaf slot
+// tagged kInstanceTag switches the lane to the instance's ray (instance.h) and the object's tree; the
+// way back is two stack entries under the object's own entries: {slots left in the parent leaf, the
+// parent's tMax} and {kReturn | next slot}.  When the object's entries are used up the return entry
+// pops: the parent ray is set up again from the ray buffer and the leaf loop resumes.  The parent
+// goes on with tMax = the t found in the object, not shifted back by dt, as the reference does.
+constexpr int kReturn = int(0x80000000u);
+template <bool ANY, bool COUNT, bool INTERNAL, bool INST>
 __global__ void __launch_bounds__(kBlock)
 TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200pt_hit *__restrict__ hits,
                       unsigned char *__restrict__ occluded, int *__restrict__ rayCounter,
@@ -74,23 +82,52 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
     RayCtx r;
     float tMax = 0, bestB0 = 0, bestB1 = 0, bestB2 = 0;
     int cur = 0, sp = 0, bestSlot = -1;
+    int lslot = 0, lrem = 0;                 // leaf cursor: next slot, slots left (0 = read the leaf header)
+    int curInst = -1, bestInst = -1;         // instance being traversed / instance of the best hit
+    bool instHit = false;                    // a hit was accepted inside the current instance
     unsigned long long cNodes = 0, cLeaves = 0, cPrims = 0;
 
-    auto push = [&](int ref, float t) {
-        int2 e = make_int2(ref, __float_as_int(t));
+    auto push = [&](int ref, int tbits) {
+        int2 e = make_int2(ref, tbits);
         if (sp < kSmemDepth) stack[sp * kBlock] = e;
         else deep[sp - kSmemDepth] = e;
         ++sp;
+    };
+    auto pop = [&]() {
+        --sp;
+        return sp < kSmemDepth ? stack[sp * kBlock] : deep[sp - kSmemDepth];
+    };
+    auto enter = [&](int ref) {
+        cur = ref;
+        if (ref < 0) {
+            state = S_LEAF;
+            lslot = ~ref;
+            lrem = 0;
+        } else {
+            state = S_NODE;
+        }
     };
     // next entry whose box the reference would still enter with the current tMax; S_DONE if none
     auto popNext = [&]() {
         state = S_DONE;
         while (sp > 0) {
-            --sp;
-            int2 e = sp < kSmemDepth ? stack[sp * kBlock] : deep[sp - kSmemDepth];
+            int2 e = pop();
+            if (INST && e.x < -(1 << 30)) {  // the way back out of an instance
+                int2 saved = pop();
+                const float *q = rays + 7ll * rayIdx;
+                RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
+                if (!instHit) tMax = __int_as_float(saved.y);
+                curInst = -1;
+                if (saved.x > 0) {
+                    state = S_LEAF;
+                    lslot = e.x & 0x3fffffff;
+                    lrem = saved.x;
+                    break;
+                }
+                continue;
+            }
             if (__int_as_float(e.y) < tMax) {
-                cur = e.x;
-                state = e.x < 0 ? S_LEAF : S_NODE;
+                enter(e.x);
                 break;
             }
         }
@@ -115,14 +152,12 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                         rayIdx = my;
                         sp = 0;
                         bestSlot = -1;
+                        curInst = -1;
+                        bestInst = -1;
                         // the reference tests the root's own box first (cpu/aggregates.cpp:545)
                         if (COUNT) ++cNodes;
-                        if (SlabTest(r, sc.rootBox, sc.rootBox + 3, tMax)) {
-                            cur = sc.rootRef;
-                            state = cur < 0 ? S_LEAF : S_NODE;
-                        } else {
-                            state = S_DONE;
-                        }
+                        if (SlabTest(r, sc.rootBox, sc.rootBox + 3, tMax)) enter(sc.rootRef);
+                        else state = S_DONE;
                     }
                 }
                 idle = __ballot_sync(FULL, state == S_IDLE);
@@ -149,27 +184,48 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                 // near child: visited now, so the whole test applies now.  far child: stacked on the
                 // tMax-independent part only; `tFar < tMax` is decided when it is popped (popNext).
                 bool hNear = (neg ? h1 : h0) & (tNear < tMax), hFar = neg ? h0 : h1;
-                if (hNear) {
-                    if (hFar) push(farRef, tFar);
-                    cur = nearRef;
-                    state = nearRef < 0 ? S_LEAF : S_NODE;
-                } else {
-                    if (hFar) push(farRef, tFar);
-                    popNext();
-                }
+                if (hFar) push(farRef, __float_as_int(tFar));
+                if (hNear) enter(nearRef);
+                else popNext();
             }
             inNode = __ballot_sync(FULL, state == S_NODE);
         } while (__popc(inNode) >= kNodeMin);
 
         // ---- leaves: triangle tests, in slot order, later equal-t hit replaces earlier
         if (state == S_LEAF) {
-            if (COUNT) ++cLeaves;
-            bool anyHit = false;
-            int slot = ~cur, leafN = 1;
-            for (int k = 0; k < leafN; ++k, ++slot) {
+            if (COUNT && lrem == 0) ++cLeaves;
+            bool anyHit = false, entered = false;
+            int slot = lslot, left = lrem;
+            while (true) {
                 Node8f a = Load256(prims + 64ll * slot);
                 float4 b = __ldg(reinterpret_cast<const float4 *>(prims + 64ll * slot + 32));
-                if (k == 0) leafN = __float_as_int(b.w);  // leaf header: count in the first slot
+                if (left == 0) left = __float_as_int(b.w);  // leaf header: count in the first slot
+                if (INST && __float_as_uint(b.y) == kInstanceTag) {
+                    const InstanceDev *in = sc.instances + __float_as_int(b.z);
+                    push(left - 1, __float_as_int(tMax));
+                    push(kReturn | (slot + 1), 0);
+                    const float4 *mi = reinterpret_cast<const float4 *>(in->mInv);
+                    float4 r0 = __ldg(mi), r1 = __ldg(mi + 1), r2 = __ldg(mi + 2);
+                    float mInv[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
+                    float o2[3], d2[3], tMax2;
+                    InstanceRay(mInv, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, tMax, o2, d2, tMax2);
+                    RaySetup(r, o2[0], o2[1], o2[2], d2[0], d2[1], d2[2]);
+                    tMax = tMax2;
+                    curInst = __float_as_int(b.z);
+                    instHit = false;
+                    int rootRef = __ldg(&in->rootRef);
+                    bool go = true;
+                    if (rootRef >= 0) {  // a one-primitive object has no BVH and no box test
+                        float box[6];
+                        for (int k = 0; k < 6; ++k) box[k] = __ldg(&in->rootBox[k]);
+                        if (COUNT) ++cNodes;
+                        go = SlabTest(r, box, box + 3, tMax);
+                    }
+                    if (go) enter(rootRef);
+                    else popNext();
+                    entered = true;
+                    break;
+                }
                 float p0[3] = {a.v[0], a.v[1], a.v[2]}, p1[3] = {a.v[3], a.v[4], a.v[5]},
                       p2[3] = {a.v[6], a.v[7], b.x};
                 float t, b0, b1, b2;
@@ -181,16 +237,24 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                     }
                     tMax = t;
                     bestSlot = slot;
+                    if (INST) {
+                        bestInst = curInst;
+                        instHit = true;
+                    }
                     if (INTERNAL) bestB0 = b0;
                     bestB1 = b1;
                     bestB2 = b2;
                 }
+                if (--left == 0) break;
+                ++slot;
             }
-            if (ANY && anyHit) {
-                bestSlot = 0;
-                state = S_DONE;
-            } else {
-                popNext();
+            if (!entered) {
+                if (ANY && anyHit) {
+                    bestSlot = 0;
+                    state = S_DONE;
+                } else {
+                    popNext();
+                }
             }
         }
         __syncwarp();
@@ -208,11 +272,12 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                 } else if (INTERNAL) {
                     w0 = make_uint2((unsigned)bestSlot, __float_as_uint(tMax));
                     w1 = make_uint2(__float_as_uint(bestB0), __float_as_uint(bestB1));
-                    w2 = make_uint2(__float_as_uint(bestB2), 0u);
+                    w2 = make_uint2(__float_as_uint(bestB2), INST ? unsigned(bestInst + 1) : 0u);
                 } else {
                     float4 b = __ldg(reinterpret_cast<const float4 *>(prims + 64ll * bestSlot + 32));
+                    // instanceId is the 1-based position in the instance list (scene.cpp:1560)
                     w0 = make_uint2(__float_as_uint(b.y), __float_as_uint(b.z));
-                    w1 = make_uint2(0u, __float_as_uint(tMax));
+                    w1 = make_uint2(INST ? unsigned(bestInst + 1) : 0u, __float_as_uint(tMax));
                     w2 = make_uint2(__float_as_uint(bestB1), __float_as_uint(bestB2));
                 }
                 uint2 *dst = reinterpret_cast<uint2 *>(hits + rayIdx);
@@ -254,14 +319,24 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
                                                   nodeMin, nDev);
         return cudaGetLastError();
     };
+    if (sc.nInstances) {
+        if (any)
+            return counters ? pick(TraversePersistKernel<true, true, false, true>)
+                            : pick(TraversePersistKernel<true, false, false, true>);
+        if (internalHits)
+            return counters ? pick(TraversePersistKernel<false, true, true, true>)
+                            : pick(TraversePersistKernel<false, false, true, true>);
+        return counters ? pick(TraversePersistKernel<false, true, false, true>)
+                        : pick(TraversePersistKernel<false, false, false, true>);
+    }
     if (any)
-        return counters ? pick(TraversePersistKernel<true, true, false>)
-                        : pick(TraversePersistKernel<true, false, false>);
+        return counters ? pick(TraversePersistKernel<true, true, false, false>)
+                        : pick(TraversePersistKernel<true, false, false, false>);
     if (internalHits)
-        return counters ? pick(TraversePersistKernel<false, true, true>)
-                        : pick(TraversePersistKernel<false, false, true>);
-    return counters ? pick(TraversePersistKernel<false, true, false>)
-                    : pick(TraversePersistKernel<false, false, false>);
+        return counters ? pick(TraversePersistKernel<false, true, true, false>)
+                        : pick(TraversePersistKernel<false, false, true, false>);
+    return counters ? pick(TraversePersistKernel<false, true, false, false>)
+                    : pick(TraversePersistKernel<false, false, false, false>);
 }
 
 }  // namespace b200pt

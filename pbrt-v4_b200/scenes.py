@@ -90,6 +90,50 @@ def random_soup(n_tris=1_000_000, seed=12111, s=0.01, n_meshes=1):
     return Scene(meshes)
 
 
+def instanced_scene(n_objects=4, tris_per_object=2000, n_instances=40, world_tris=3000, seed=77, s=0.05):
+    """BASELINE config 3 in miniature: object definitions (random soups in [-1/2, 1/2]^3) placed many
+    times by rotation x uniform scale x translation inside the unit cube, over a world-level soup.
+    Both matrices of each instance are stored in float32 (the host hands over pbrt's m and mInv)."""
+    rng = np.random.default_rng(seed)
+    meshes = []
+    if world_tris:
+        meshes += random_soup(world_tris, seed=seed + 1, s=0.02).meshes
+    for o in range(n_objects):
+        cnt = tris_per_object if o else 2  # object 0: the smallest BVH an object can have
+        c = rng.random((cnt, 1, 3)) - 0.5
+        v = (c + (rng.random((cnt, 3, 3)) * 2 - 1) * s).astype(np.float32)
+        meshes.append(Mesh(v.reshape(-1, 3), np.arange(3 * cnt, dtype=np.int32).reshape(-1, 3), object=o))
+    insts = []
+    for i in range(n_instances):
+        q = rng.normal(size=4)
+        q /= np.linalg.norm(q)
+        w, x, y, z = q
+        R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                      [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                      [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+        if i % 7 == 3:
+            R = np.eye(3)  # some axis-aligned placements: exact zeros in the matrices
+        sc = rng.uniform(0.08, 0.3)
+        t = rng.uniform(0.15, 0.85, 3)
+        M = np.eye(4)
+        M[:3, :3] = R * sc
+        M[:3, 3] = t
+        insts.append(Instance(i % n_objects, M.astype(np.float32), np.linalg.inv(M).astype(np.float32)))
+    return Scene(meshes, insts)
+
+
+def flattened(scene):
+    """All geometry of `scene` as world-level meshes in render space (instances applied in float64);
+    only for aiming test rays at instanced geometry."""
+    out = [m for m in scene.meshes if m.object < 0]
+    for inst in scene.instances:
+        M = inst.render_from_instance.astype(np.float64)
+        for m in scene.meshes:
+            if m.object == inst.object:
+                out.append(Mesh((m.p.astype(np.float64) @ M[:3, :3].T + M[:3, 3]).astype(np.float32), m.indices))
+    return Scene(out)
+
+
 def _quad(p0, p1, p2, p3):
     return Mesh(np.array([p0, p1, p2, p3], dtype=np.float32), np.array([[0, 1, 2], [0, 2, 3]], dtype=np.int32))
 

@@ -18,7 +18,10 @@ def cases(S):
     soup = S.random_soup(20000, seed=21, n_meshes=2)
     cb = S.cornell_box()
     sheet = S.Scene([S.grid_sheet(32, 32, jitter=0.0), S.grid_sheet(24, 24, z=0.75, jitter=0.02, seed=9)])
+    inst = S.instanced_scene(n_objects=3, tris_per_object=600, n_instances=24, world_tris=1500, seed=41)
     return {
+        "instanced_primary": (inst, S.primary_rays(30000, seed=36)),
+        "instanced_adversarial": (inst, S.adversarial_rays(S.flattened(inst), 20000, seed=37)),
         "soup20k_primary": (soup, S.primary_rays(40000, seed=31)),
         "soup20k_adversarial": (soup, S.adversarial_rays(soup, 20000, seed=32)),
         "cornell_camera": (cb, S.camera_rays(128, 128, (0.5, 0.5, -1.4), (0.5, 0.5, 0.5), spp=1)),

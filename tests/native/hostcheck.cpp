@@ -12,10 +12,135 @@
 #include <string>
 #include <vector>
 
+#include "../../pbrt-v4_b200/csrc/instance.h"
 #include "../../pbrt-v4_b200/csrc/isect.h"
 #include "../../pbrt-v4_b200/csrc/scene_host.h"
 
 using namespace b200pt;
+
+struct Best {
+    int slot = -1, inst = -1;  // inst: index into hs.instances, -1 = world geometry
+    float b1 = 0, b2 = 0;
+};
+
+// PairNode walk with the {ref, tMin} stack and the pop-time `tMin < tMax` re-check, as
+// traverse_persist.cu does it; an instance leaf recurses with the transformed ray (the device kernel
+// keeps the way back on its stack instead - same visits, same arithmetic).
+static bool TracePairs(const HostScene &hs, int rootRef, const float *rootBox, const float *o, const float *d,
+                       float &tMax, bool any, Best &best, int curInst, bool dbg) {
+    RayCtx r;
+    RaySetup(r, o[0], o[1], o[2], d[0], d[1], d[2]);
+    struct E { int ref; float t; };
+    E stack[128];
+    int sp = 0, cur = 0;
+    bool done = false;
+    auto popNext = [&]() {
+        done = true;
+        while (sp > 0) {
+            E e = stack[--sp];
+            if (e.t < tMax) { cur = e.ref; done = false; break; }
+        }
+    };
+    // a one-primitive object has no BVH and no box (scene.cpp:1551): rootBox == nullptr
+    if (!rootBox || SlabTest(r, rootBox, rootBox + 3, tMax)) cur = rootRef; else done = true;
+    while (!done) {
+        if (cur >= 0) {
+            const PairNode &pn = hs.pairs[cur];
+            float t0, t1;
+            bool h0 = SlabCore(r, pn.box0, pn.box0 + 3, t0);
+            bool h1 = SlabCore(r, pn.box1, pn.box1 + 3, t1);
+            if (dbg)
+                fprintf(stderr, "pair %d: h0 %d t0 %g ref0 %d | h1 %d t1 %g ref1 %d | tMax %.9g\n", cur, h0, t0, pn.ref0, h1, t1, pn.ref1, tMax);
+            bool neg = r.neg[pn.axis] != 0;
+            int nearRef = neg ? pn.ref1 : pn.ref0, farRef = neg ? pn.ref0 : pn.ref1;
+            float tNear = neg ? t1 : t0, tFar = neg ? t0 : t1;
+            bool hNear = (neg ? h1 : h0) && (tNear < tMax), hFar = neg ? h0 : h1;
+            if (hFar) stack[sp++] = E{farRef, tFar};
+            if (hNear) cur = nearRef;
+            else popNext();
+        } else {
+            int slot = ~cur, cnt = int(hs.prims[slot].flags);
+            for (int k = 0; k < cnt; ++k, ++slot) {
+                const PrimSlot &s = hs.prims[slot];
+                if (s.mesh == kInstanceTag) {
+                    const InstanceDev &in = hs.instances[s.tri];
+                    float o2[3], d2[3], tMax2;
+                    InstanceRay(in.mInv, o[0], o[1], o[2], d[0], d[1], d[2], tMax, o2, d2, tMax2);
+                    Best sub;
+                    bool h = TracePairs(hs, in.rootRef, in.rootRef < 0 ? nullptr : in.rootBox, o2, d2, tMax2, any, sub,
+                                        int(s.tri), dbg);
+                    if (any && h) return true;
+                    if (!any && sub.slot >= 0) {  // the parent goes on with tMax = the object's t, not shifted back
+                        tMax = tMax2;
+                        best = sub;
+                    }
+                    continue;
+                }
+                float t, b0, b1, b2;
+                if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
+                    if (any) return true;
+                    tMax = t; best.slot = slot; best.inst = curInst; best.b1 = b1; best.b2 = b2;
+                }
+            }
+            popNext();
+        }
+    }
+    return any ? false : best.slot >= 0;
+}
+
+// the reference's own loop shape over the LinearBVHNode layout (cpu/aggregates.cpp:529-579)
+static bool TraceNodes(const HostScene &hs, int root, bool testRoot, const float *o, const float *d, float &tMax,
+                       bool any, Best &best, int curInst, bool dbg) {
+    RayCtx r;
+    RaySetup(r, o[0], o[1], o[2], d[0], d[1], d[2]);
+    int stack[64], sp = 0, cur = root;
+    while (true) {
+        const Node32 &nd = hs.nodes[cur];
+        if (dbg) {
+            float tm; bool h = SlabCore(r, nd.bmin, nd.bmax, tm) && tm < tMax;
+            fprintf(stderr, "node %d: h %d tmin %g nprims %d off %d tMax %.9g\n", cur, h, tm, nd.nPrims, nd.offset, tMax);
+        }
+        if (!testRoot || SlabTest(r, nd.bmin, nd.bmax, tMax)) {
+            if (nd.nPrims > 0) {
+                for (int k = 0; k < nd.nPrims; ++k) {
+                    const PrimSlot &s = hs.prims[nd.offset + k];
+                    if (s.mesh == kInstanceTag) {
+                        const InstanceDev &in = hs.instances[s.tri];
+                        float o2[3], d2[3], tMax2;
+                        InstanceRay(in.mInv, o[0], o[1], o[2], d[0], d[1], d[2], tMax, o2, d2, tMax2);
+                        Best sub;
+                        bool h = TraceNodes(hs, int(in.rootNode), hs.nodes[in.rootNode].nPrims == 0, o2, d2, tMax2, any,
+                                            sub, int(s.tri), dbg);
+                        if (any && h) return true;
+                        if (!any && sub.slot >= 0) {
+                            tMax = tMax2;
+                            best = sub;
+                        }
+                        continue;
+                    }
+                    float t, b0, b1, b2;
+                    if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
+                        if (any) return true;
+                        tMax = t; best.slot = nd.offset + k; best.inst = curInst; best.b1 = b1; best.b2 = b2;
+                    }
+                }
+                if (sp == 0) break;
+                cur = stack[--sp];
+            } else if (r.neg[nd.axis]) {
+                stack[sp++] = cur + 1;
+                cur = nd.offset;
+            } else {
+                stack[sp++] = nd.offset;
+                cur = cur + 1;
+            }
+        } else {
+            if (sp == 0) break;
+            cur = stack[--sp];
+        }
+        testRoot = true;
+    }
+    return any ? false : best.slot >= 0;
+}
 
 int main(int argc, char **argv) {
     if (argc < 5) return 2;
@@ -33,10 +158,18 @@ int main(int argc, char **argv) {
         if (fread(I[m].data(), 4, I[m].size(), f) != I[m].size()) return 2;
         meshes[m] = b200pt_mesh{obj, nv, nt, P[m].data(), I[m].data()};
     }
+    std::vector<b200pt_instance> insts(hdr[3]);
+    for (uint32_t i = 0; i < hdr[3]; ++i) {
+        if (fread(&insts[i].object, 4, 1, f) != 1 || fread(insts[i].render_from_instance, 4, 16, f) != 16 ||
+            fread(insts[i].instance_from_render, 4, 16, f) != 16)
+            return 2;
+    }
     fclose(f);
     b200pt_scene_desc desc{};
     desc.n_meshes = hdr[2];
     desc.meshes = meshes.data();
+    desc.n_instances = hdr[3];
+    desc.instances = insts.data();
     HostScene hs;
     std::string err;
     if (AssembleScene(&desc, hs, err) != 0) { fprintf(stderr, "%s\n", err.c_str()); return 3; }
@@ -52,98 +185,18 @@ int main(int argc, char **argv) {
     bool pairMode = mode == "closest2" || mode == "any2";
     std::vector<b200pt_hit> hits(any ? 0 : n);
     std::vector<uint8_t> occ(any ? n : 0);
-    for (size_t i = 0; pairMode && i < n; ++i) {
+    for (size_t i = 0; i < n; ++i) {
         const float *q = &rays[7 * i];
-        RayCtx r;
-        RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
         float tMax = q[6];
-        struct E { int ref; float t; };
-        E stack[128];
-        int sp = 0, cur = 0, best = -1;
-        float bb1 = 0, bb2 = 0;
-        bool hitAny = false, done = false;
-        auto popNext = [&]() {
-            done = true;
-            while (sp > 0) {
-                E e = stack[--sp];
-                if (e.t < tMax) { cur = e.ref; done = false; break; }
-            }
-        };
-        if (SlabTest(r, hs.bounds, hs.bounds + 3, tMax)) cur = hs.rootRef; else done = true;
-        while (!done) {
-            if (cur >= 0) {
-                const PairNode &pn = hs.pairs[cur];
-                float t0, t1;
-                bool h0 = SlabCore(r, pn.box0, pn.box0 + 3, t0);
-                bool h1 = SlabCore(r, pn.box1, pn.box1 + 3, t1);
-                if (getenv("RAYDBG") && (size_t)atol(getenv("RAYDBG")) == i)
-                    fprintf(stderr, "pair %d: h0 %d t0 %g ref0 %d | h1 %d t1 %g ref1 %d | tMax %.9g\n", cur, h0, t0, pn.ref0, h1, t1, pn.ref1, tMax);
-                bool neg = r.neg[pn.axis] != 0;
-                int nearRef = neg ? pn.ref1 : pn.ref0, farRef = neg ? pn.ref0 : pn.ref1;
-                float tNear = neg ? t1 : t0, tFar = neg ? t0 : t1;
-                bool hNear = (neg ? h1 : h0) && (tNear < tMax), hFar = neg ? h0 : h1;
-                if (hFar) stack[sp++] = E{farRef, tFar};
-                if (hNear) cur = nearRef;
-                else popNext();
-            } else {
-                int slot = ~cur, cnt = int(hs.prims[slot].flags);
-                for (int k = 0; k < cnt; ++k, ++slot) {
-                    const PrimSlot &s = hs.prims[slot];
-                    float t, b0, b1, b2;
-                    if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
-                        if (any) { hitAny = true; break; }
-                        tMax = t; best = slot; bb1 = b1; bb2 = b2;
-                    }
-                }
-                if (hitAny) break;
-                popNext();
-            }
-        }
-        if (any) occ[i] = hitAny;
-        else if (best < 0) hits[i] = b200pt_hit{0xFFFFFFFFu, 0, 0, 0, 0, 0};
-        else hits[i] = b200pt_hit{hs.prims[best].mesh, hs.prims[best].tri, 0, tMax, bb1, bb2};
-    }
-    for (size_t i = 0; !pairMode && i < n; ++i) {
-        const float *q = &rays[7 * i];
-        RayCtx r;
-        RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
-        float tMax = q[6];
-        int stack[64], sp = 0, cur = int(hs.rootNode), best = -1;
-        float bb1 = 0, bb2 = 0;
-        bool hitAny = false;
-        while (true) {
-            const Node32 &nd = hs.nodes[cur];
-            if (getenv("RAYDBG") && (size_t)atol(getenv("RAYDBG")) == i) {
-                float tm; bool h = SlabCore(r, nd.bmin, nd.bmax, tm) && tm < tMax;
-                fprintf(stderr, "node %d: h %d tmin %g nprims %d off %d tMax %.9g\n", cur, h, tm, nd.nPrims, nd.offset, tMax);
-            }
-            if (SlabTest(r, nd.bmin, nd.bmax, tMax)) {
-                if (nd.nPrims > 0) {
-                    for (int k = 0; k < nd.nPrims && !hitAny; ++k) {
-                        const PrimSlot &s = hs.prims[nd.offset + k];
-                        float t, b0, b1, b2;
-                        if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
-                            if (any) { hitAny = true; break; }
-                            tMax = t; best = nd.offset + k; bb1 = b1; bb2 = b2;
-                        }
-                    }
-                    if (hitAny || sp == 0) break;
-                    cur = stack[--sp];
-                } else if (r.neg[nd.axis]) {
-                    stack[sp++] = cur + 1;
-                    cur = nd.offset;
-                } else {
-                    stack[sp++] = nd.offset;
-                    cur = cur + 1;
-                }
-            } else {
-                if (sp == 0) break;
-                cur = stack[--sp];
-            }
-        }
-        if (any) occ[i] = hitAny;
-        else if (best < 0) hits[i] = b200pt_hit{0xFFFFFFFFu, 0, 0, 0, 0, 0};
-        else hits[i] = b200pt_hit{hs.prims[best].mesh, hs.prims[best].tri, 0, tMax, bb1, bb2};
+        bool dbg = getenv("RAYDBG") && (size_t)atol(getenv("RAYDBG")) == i;
+        Best best;
+        bool h = pairMode ? TracePairs(hs, hs.rootRef, hs.bounds, q, q + 3, tMax, any, best, -1, dbg)
+                          : TraceNodes(hs, int(hs.rootNode), true, q, q + 3, tMax, any, best, -1, dbg);
+        if (any) occ[i] = h;
+        else if (best.slot < 0) hits[i] = b200pt_hit{0xFFFFFFFFu, 0, 0, 0, 0, 0};
+        else
+            hits[i] = b200pt_hit{hs.prims[best.slot].mesh, hs.prims[best.slot].tri,
+                                 best.inst < 0 ? 0u : hs.instances[best.inst].instanceId, tMax, best.b1, best.b2};
     }
     FILE *of = fopen(argv[4], "wb");
     if (any) fwrite(occ.data(), 1, n, of); else fwrite(hits.data(), sizeof(b200pt_hit), n, of);

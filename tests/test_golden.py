@@ -13,7 +13,8 @@ from test_hostcheck import run_hostcheck
 _spec = importlib.util.spec_from_file_location("make_golden", os.path.join(ROOT, "tests", "golden", "make_golden.py"))
 G = importlib.util.module_from_spec(_spec)
 _spec.loader.exec_module(G)
-NAMES = ["soup20k_primary", "soup20k_adversarial", "cornell_camera", "cornell_adversarial", "sheets_adversarial"]
+NAMES = ["soup20k_primary", "soup20k_adversarial", "cornell_camera", "cornell_adversarial", "sheets_adversarial",
+         "instanced_primary", "instanced_adversarial"]
 
 
 @pytest.mark.parametrize("name", NAMES)

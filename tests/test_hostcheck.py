@@ -29,6 +29,10 @@ CASES = {
     "cornell_adversarial": lambda S: (S.cornell_box(), "adversarial"),
     "sheet_adversarial": lambda S: (S.Scene([S.grid_sheet(64, 64, jitter=0.01)]), "adversarial"),
     "flat_sheet_adversarial": lambda S: (S.Scene([S.grid_sheet(32, 32, jitter=0.0)]), "adversarial"),
+    # object instances (TransformedPrimitive, cpu/primitive.cpp:112-131): interval ray transform, t not shifted back
+    "instanced_primary": lambda S: (S.instanced_scene(), "primary"),
+    "instanced_adversarial": lambda S: (S.instanced_scene(seed=78), "adversarial"),
+    "instanced_only": lambda S: (S.instanced_scene(n_instances=12, world_tris=0, seed=79), "adversarial"),
 }
 
 
@@ -42,12 +46,14 @@ def test_host_arithmetic_bit_exact(P, refrun, hostcheck_bin, case, layout):
     elif kind == "camera":
         rays = S.camera_rays(192, 192, (0.5, 0.5, -1.4), (0.5, 0.5, 0.5), spp=2)
     else:
-        rays = S.adversarial_rays(sc, 100000)
+        rays = S.adversarial_rays(S.flattened(sc), 100000)
     rs = refrun.RefScene(sc)
     ref, _ = rs.closest(rays)
     occ_ref, _ = rs.any(rays)
     mine, occ = run_hostcheck(hostcheck_bin, P, rs, rays, layout)
     assert (ref["mesh"] != 0xFFFFFFFF).mean() > 0.3
+    if sc.instances:
+        assert (ref["instance"] != 0).mean() > 0.2
     assert hit_mismatches(mine, ref).sum() == 0
     assert (occ != occ_ref).sum() == 0
     # shadow rays from the hit points (unnormalised d, tMax = 1 - 1e-4)

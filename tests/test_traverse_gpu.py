@@ -15,7 +15,8 @@ pytestmark = pytest.mark.gpu
 _spec = importlib.util.spec_from_file_location("make_golden", os.path.join(ROOT, "tests", "golden", "make_golden.py"))
 G = importlib.util.module_from_spec(_spec)
 _spec.loader.exec_module(G)
-NAMES = ["soup20k_primary", "soup20k_adversarial", "cornell_camera", "cornell_adversarial", "sheets_adversarial"]
+NAMES = ["soup20k_primary", "soup20k_adversarial", "cornell_camera", "cornell_adversarial", "sheets_adversarial",
+         "instanced_primary", "instanced_adversarial"]
 
 
 @pytest.mark.parametrize("name", NAMES)
@@ -29,8 +30,11 @@ def test_gpu_matches_golden(P, name):
     sh = P.scenes.shadow_rays(rays, gold["hits"], seed=35)
     assert hit_mismatches(agg.IntersectClosest(sh), gold["shadow_hits"]).sum() == 0
     assert np.array_equal(agg.IntersectShadow(sh), gold["shadow_occ"])
-    assert np.array_equal(agg.Bounds().reshape(-1),
-                          np.concatenate([sc.triangle_boxes()[:, :3].min(0), sc.triangle_boxes()[:, 3:].max(0)]))
+    if not sc.instances:
+        assert np.array_equal(agg.Bounds().reshape(-1),
+                              np.concatenate([sc.triangle_boxes()[:, :3].min(0), sc.triangle_boxes()[:, 3:].max(0)]))
+    else:
+        assert (hits["instance"] != 0).mean() > 0.1
     agg.close()
 
 
@@ -46,6 +50,31 @@ def test_gpu_matches_reference_200k_soup(P, refrun):
         occ_ref, _ = rs.any(sh)
         assert (agg.IntersectShadow(sh) != occ_ref).sum() == 0
     agg.close()
+
+
+def test_gpu_instances_match_reference(P, refrun):
+    """Object instances: 8 objects x up to 20 K triangles placed 200 times over a world soup,
+    own trees and the trees read out of the reference, primary + adversarial + shadow batches."""
+    sc = P.scenes.instanced_scene(n_objects=8, tris_per_object=20000, n_instances=200, world_tris=50000, seed=91)
+    rs = refrun.RefScene(sc)
+    own = P.B200Aggregate(sc)
+    given = P.B200Aggregate(sc, bvhs=rs.dump_bvh())
+    assert own.stats()["n_instances"] == 200
+    for rays in (P.scenes.primary_rays(1 << 19, seed=3), P.scenes.adversarial_rays(P.scenes.flattened(sc), 1 << 17, seed=4)):
+        ref, _ = rs.closest(rays)
+        mine = own.IntersectClosest(rays)
+        assert (ref["instance"] != 0).mean() > 0.2
+        assert hit_mismatches(mine, ref).sum() == 0
+        assert np.array_equal(mine.view("u1"), given.IntersectClosest(rays).view("u1"))
+        occ_ref, _ = rs.any(rays)
+        assert (own.IntersectShadow(rays) != occ_ref).sum() == 0
+        sh = P.scenes.shadow_rays(rays, mine)
+        ref_sh, _ = rs.closest(sh)
+        occ_sh, _ = rs.any(sh)
+        assert hit_mismatches(own.IntersectClosest(sh), ref_sh).sum() == 0
+        assert (own.IntersectShadow(sh) != occ_sh).sum() == 0
+    own.close()
+    given.close()
 
 
 def test_gpu_with_host_supplied_bvh(P, refrun):
