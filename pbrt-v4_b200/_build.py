@@ -62,7 +62,7 @@ def build(verbose=False, force=False):
         objs.append(obj)
         if force or _newer(src, obj, headers):
             _run([NVCC, "-std=c++17", "-O3", "-lineinfo", "-Xptxas", "-v", "-Xcompiler", "-fPIC",
-                  "-Xcompiler", "-ffp-contract=off"] + GENCODE + extra + ["-c", src, "-o", obj], verbose)
+                  "-Xcompiler", "-ffp-contract=off"] + GENCODE + extra + os.environ.get("B200PT_NVCC_EXTRA", "").split() + ["-c", src, "-o", obj], verbose)
     if force or any(_newer(o, LIB, []) for o in objs):
         _run([NVCC, "-shared", "-o", LIB] + objs + GENCODE + ["-cudart", "static"], verbose)
     return LIB

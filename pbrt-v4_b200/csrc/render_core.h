@@ -125,8 +125,6 @@ B2_HD float SobolSampleZ(uint64_t a, int dim, uint32_t randomize, uint32_t hash)
     else if (randomize == 3) v = OwenScramble(v, hash);
     return fminf(v * 0x1p-32f, kOneMinusEps);
 }
-// (not inlined on the device: the shading kernels call these five or six times per vertex and the
-// code would otherwise be replicated at every call site)
 B2_HD_NOINLINE float ZSobolGet1D(ZSobol &s) {  // samplers.h:258-272
     uint64_t idx = ZSobolSampleIndex(s);
     ++s.dimension;
