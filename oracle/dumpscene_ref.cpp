@@ -271,7 +271,9 @@ int main(int argc, char **argv) {
     for (size_t i = 0; i < lights.size(); ++i) lightIndex[lights[i].ptr()] = int(i);
     std::vector<uint32_t> bvhPrims;
     std::vector<int32_t> lightMeshTri(lights.size() * 2, -1);
-    for (const Primitive &p : bvh->primitives) {
+    std::vector<int32_t> meshObject(nMesh, -1);
+    // one triangle primitive of the world or of an object definition -> its mesh / material / light records
+    auto visitTriangle = [&](const Primitive &p, int object, std::vector<uint32_t> &primsOut) {
         Shape shape;
         pbrt::Material mtl;
         Light area;
@@ -288,11 +290,13 @@ int main(int argc, char **argv) {
         if (!shape.Is<Triangle>()) die("only triangles are dumped so far");
         const Triangle *t = shape.Cast<Triangle>();
         int m = t->meshIndex;
-        bvhPrims.insert(bvhPrims.end(), {0u, uint32_t(m), uint32_t(t->triIndex)});
+        primsOut.insert(primsOut.end(), {0u, uint32_t(m), uint32_t(t->triIndex)});
         if (!materialId.count(mtl.ptr())) {
             materialId[mtl.ptr()] = int(materialList.size());
             materialList.push_back(mtl);
         }
+        if (meshObject[m] != -1 && meshObject[m] != object) die("mesh used by two object definitions");
+        meshObject[m] = object;
         meshAttr[3 * m + 0] = mtl ? materialId[mtl.ptr()] : -1;
         meshAttr[3 * m + 2] = (allMeshes[m]->reverseOrientation ^ allMeshes[m]->transformSwapsHandedness) ? 1 : 0;
         if (area) {
@@ -303,13 +307,60 @@ int main(int argc, char **argv) {
             if (meshAttr[3 * m + 1] != -1 && meshAttr[3 * m + 1] != first) die("area lights of a mesh are not consecutive");
             meshAttr[3 * m + 1] = first;
         }
+    };
+    // object definitions met through TransformedPrimitives (scene.cpp:1523-1575)
+    std::map<const void *, int> objectId;
+    std::vector<std::vector<uint32_t>> objNodes, objPrims;
+    std::vector<int32_t> instObject;
+    std::vector<float> instM, instMInv;
+    std::map<int, std::pair<int, const Transform *>> instById;
+    for (const Primitive &p : bvh->primitives) {
+        const TransformedPrimitive *tp = p.CastOrNullptr<TransformedPrimitive>();
+        if (!tp) {
+            visitTriangle(p, -2, bvhPrims);  // -2 = world (kept apart from "unseen" = -1 until the remap below)
+            continue;
+        }
+        const void *key = tp->primitive.ptr();
+        if (!objectId.count(key)) {
+            int id = int(objectId.size());
+            objectId[key] = id;
+            objNodes.emplace_back();
+            objPrims.emplace_back();
+            if (const BVHAggregate *ob = tp->primitive.CastOrNullptr<BVHAggregate>()) {
+                for (const Primitive &q : ob->primitives) visitTriangle(q, id, objPrims[id]);
+                int nn = countNodes(ob->nodes);
+                objNodes[id].resize(size_t(nn) * 8);
+                memcpy(objNodes[id].data(), ob->nodes, size_t(nn) * 32);
+            } else {
+                // a one-primitive object has no BVH (scene.cpp:1551): hand over a one-leaf tree of its bounds
+                visitTriangle(tp->primitive, id, objPrims[id]);
+                Bounds3f bb = tp->primitive.Bounds();
+                LinearBVHNode leaf;
+                memset(&leaf, 0, sizeof leaf);
+                leaf.bounds = bb;
+                leaf.primitivesOffset = 0;
+                leaf.nPrimitives = 1;
+                objNodes[id].resize(8);
+                memcpy(objNodes[id].data(), &leaf, 32);
+            }
+        }
+        bvhPrims.insert(bvhPrims.end(), {1u, tp->instanceId, 0u});
+        instById[int(tp->instanceId)] = {objectId[key], tp->renderFromPrimitive};
+    }
+    for (size_t k = 0; k < instById.size(); ++k) {
+        auto it = instById.find(int(k) + 1);
+        if (it == instById.end()) die("instance ids are not 1..n (empty instances are not handled)");
+        instObject.push_back(it->second.first);
+        std::vector<float> a = Mat(it->second.second->GetMatrix()), b = Mat(it->second.second->GetInverseMatrix());
+        instM.insert(instM.end(), a.begin(), a.end());
+        instMInv.insert(instMInv.end(), b.begin(), b.end());
     }
     // Meshes that no primitive of the aggregate refers to (the private shape copies the area
     // lights keep) are left out; the rest are renumbered densely.
     std::vector<int> meshRemap(nMesh, -1);
     {
         std::vector<char> used(nMesh, 0);
-        for (size_t i = 0; i < bvhPrims.size(); i += 3) used[bvhPrims[i + 1]] = 1;
+        for (size_t m = 0; m < nMesh; ++m) used[m] = meshObject[m] != -1;
         int next = 0;
         for (size_t m = 0; m < nMesh; ++m)
             if (used[m]) meshRemap[m] = next++;
@@ -317,7 +368,14 @@ int main(int argc, char **argv) {
         for (size_t m = 0; m < nMesh; ++m)
             if (used[m]) memcpy(&attr2[3 * meshRemap[m]], &meshAttr[3 * m], 12);
         meshAttr.swap(attr2);
-        for (size_t i = 0; i < bvhPrims.size(); i += 3) bvhPrims[i + 1] = meshRemap[bvhPrims[i + 1]];
+        for (size_t i = 0; i < bvhPrims.size(); i += 3)
+            if (bvhPrims[i] == 0) bvhPrims[i + 1] = meshRemap[bvhPrims[i + 1]];
+        for (auto &op : objPrims)
+            for (size_t i = 0; i < op.size(); i += 3) op[i + 1] = meshRemap[op[i + 1]];
+        std::vector<int32_t> mo2(next);
+        for (size_t m = 0; m < nMesh; ++m)
+            if (used[m]) mo2[meshRemap[m]] = meshObject[m] == -2 ? -1 : meshObject[m];
+        meshObject.swap(mo2);
         for (size_t i = 0; i < lightMeshTri.size(); i += 2)
             if (lightMeshTri[i] >= 0) lightMeshTri[i] = meshRemap[lightMeshTri[i]];
     }
@@ -340,6 +398,16 @@ int main(int argc, char **argv) {
     w.f32("P", {uint32_t(P.size() / 3), 3}, P);
     w.i32("indices", {uint32_t(idx.size() / 3), 3}, idx);
     w.i32("mesh_attr", {uint32_t(nMesh), 3}, meshAttr);
+    w.i32("mesh_object", {uint32_t(nMesh)}, meshObject);
+    if (!instObject.empty()) {
+        w.i32("instance_object", {uint32_t(instObject.size())}, instObject);
+        w.f32("instance_m", {uint32_t(instObject.size()), 16}, instM);
+        w.f32("instance_minv", {uint32_t(instObject.size()), 16}, instMInv);
+        for (size_t k = 0; k < objNodes.size(); ++k) {
+            w.u32("obj_bvh_nodes_" + std::to_string(k), {uint32_t(objNodes[k].size() / 8), 8}, objNodes[k]);
+            w.u32("obj_bvh_prims_" + std::to_string(k), {uint32_t(objPrims[k].size() / 3), 3}, objPrims[k]);
+        }
+    }
     int nNodes = countNodes(bvh->nodes);
     std::vector<uint32_t> nodeWords(size_t(nNodes) * 8);
     memcpy(nodeWords.data(), bvh->nodes, size_t(nNodes) * 32);

@@ -41,8 +41,8 @@ static_assert(sizeof(PairNode) == 64, "PairNode is two 32-byte loads");
 
 // One entry per object instance (TransformedPrimitive, cpu/primitive.cpp:112-131).
 struct alignas(16) InstanceDev {
-    float mInv[12];      // instanceFromRender rows 0..2 (the ray goes through this: instance.h)
-    float m[12];         // renderFromInstance rows 0..2 (the hit comes back through this)
+    float mInv[16];      // instanceFromRender, row major (the ray goes through this: instance.h)
+    float m[16];         // renderFromInstance (the hit comes back through this)
     float rootBox[6];    // bounds of the object's BVH root, object space
     int32_t rootRef;     // PairNode index of the object's root, or ~slot when the object is one primitive
                          // (then there is no BVH and no box test: scene.cpp:1542-1551)
@@ -51,7 +51,7 @@ struct alignas(16) InstanceDev {
     uint32_t object;
     uint32_t pad[2];
 };
-static_assert(sizeof(InstanceDev) == 144, "InstanceDev layout");
+static_assert(sizeof(InstanceDev) == 176, "InstanceDev layout");
 
 struct DeviceScene {
     const void *nodes;   // Node32[], 32 B, child/prim offsets absolute (parity kernel)

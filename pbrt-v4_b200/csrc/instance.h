@@ -34,7 +34,9 @@ B2_HD float NextFloatDown32(float v) {  // util/float.h:158-172
     return v;
 }
 
-// mInv: rows 0..2 of instanceFromRender, row major, 4 floats per row.
+// mInv: instanceFromRender, row major 4x4.  pbrt inverts instance matrices numerically, so the last row
+// is often (0, 0, 0, 1 - 1ulp): the reference then divides the point interval by wp (transform.cpp:300-302,
+// util/math.h:1028-1036), which is reproduced.
 B2_HD void InstanceRay(const float *mInv, float ox, float oy, float oz, float dx, float dy, float dz, float tMax,
                        float o2[3], float d2[3], float &tMax2) {
     const float g3 = GammaF(3);
@@ -55,6 +57,30 @@ B2_HD void InstanceRay(const float *mInv, float ox, float oy, float oz, float dx
             hi[r] = NextFloatUp32(B2_ADD(p, err));
         }
         d2[r] = B2_ADD(B2_ADD(B2_MUL(m[0], dx), B2_MUL(m[1], dy)), B2_MUL(m[2], dz));
+    }
+    {
+        const float *m = mInv + 12;
+        float wp = B2_ADD(B2_ADD(B2_MUL(m[0], ox), B2_MUL(m[1], oy)), B2_ADD(B2_MUL(m[2], oz), m[3]));
+        if (wp != 1) {
+            for (int r = 0; r < 3; ++r) {
+                float a = lo[r], b = hi[r];
+                if (wp == 0) {
+                    lo[r] = -INFINITY;
+                    hi[r] = INFINITY;
+                } else if (wp > 0) {
+                    lo[r] = NextFloatDown32(B2_DIV(a, wp));
+                    hi[r] = NextFloatUp32(B2_DIV(b, wp));
+                } else {
+                    lo[r] = NextFloatDown32(B2_DIV(b, wp));
+                    hi[r] = NextFloatUp32(B2_DIV(a, wp));
+                }
+                if (lo[r] > hi[r]) {  // Interval(low, high) orders its ends
+                    float t = lo[r];
+                    lo[r] = hi[r];
+                    hi[r] = t;
+                }
+            }
+        }
     }
     float lengthSquared = B2_ADD(B2_ADD(B2_MUL(d2[0], d2[0]), B2_MUL(d2[1], d2[1])), B2_MUL(d2[2], d2[2]));
     tMax2 = tMax;

@@ -99,6 +99,7 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     r->dev.lights = (const LightDev *)r->dLights;
     r->dev.meshes = (const MeshAttrDev *)r->dMeshes;
     r->dev.prims = scene->dev.prims;
+    r->dev.instances = scene->dev.instances;
     for (const MaterialDev &m : r->host.materials) r->matMask |= 1u << m.type;
     for (const MeshAttrDev &m : r->host.meshes)
         if (m.material < 0) r->matMask |= 1u;  // null materials go through the diffuse queue, which ends the path

@@ -165,7 +165,20 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
     TriVerts tv = LoadTri(rs.prims, slot);
     const MeshAttrDev mesh = rs.meshes[tv.mesh];
     V3 wo = -p.rayD;
-    SurfHit si = TriangleInteraction(tv, b0, b1, b2, wo, mesh.flipNormal != 0);
+    SurfHit si;
+    if (hit[5] != 0) {
+        // hit inside an object instance: the interaction is built in the object's space from the
+        // instance ray (cpu/primitive.cpp:116-125) and transformed back
+        const InstanceDev &in = reinterpret_cast<const InstanceDev *>(rs.instances)[hit[5] - 1];
+        const float *mi = in.mInv;
+        V3 dInst = mk(mi[0] * p.rayD.x + mi[1] * p.rayD.y + mi[2] * p.rayD.z,
+                      mi[4] * p.rayD.x + mi[5] * p.rayD.y + mi[6] * p.rayD.z,
+                      mi[8] * p.rayD.x + mi[9] * p.rayD.y + mi[10] * p.rayD.z);
+        si = TriangleInteraction(tv, b0, b1, b2, -dInst, mesh.flipNormal != 0);
+        TransformSurfHit(in, si);
+    } else {
+        si = TriangleInteraction(tv, b0, b1, b2, wo, mesh.flipNormal != 0);
+    }
 
     // ---- emitted light at the hit (cpu/integrators.cpp:664-679)
     if (mesh.lightFirst >= 0) {

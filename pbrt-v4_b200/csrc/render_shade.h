@@ -63,6 +63,43 @@ B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b
     return h;
 }
 
+// Transform::operator()(SurfaceInteraction) for an object instance (util/transform.cpp:227-258,
+// util/transform.h:133-176, 329-334): the hit found in the object's space goes back to render space.
+B2_HD void TransformSurfHit(const InstanceDev &in, SurfHit &h) {
+    const float *m = in.m, *mi = in.mInv;
+    V3 p = Mid(h.pi), e = Err(h.pi);
+    const float g3 = GammaF(3);
+    float q[3], qe[3];
+    for (int r = 0; r < 3; ++r) {
+        const float *row = m + 4 * r;
+        q[r] = (row[0] * p.x + row[1] * p.y) + (row[2] * p.z + row[3]);
+        qe[r] = (g3 + 1) * (fabsf(row[0]) * e.x + fabsf(row[1]) * e.y + fabsf(row[2]) * e.z) +
+                g3 * (fabsf(row[0] * p.x) + fabsf(row[1] * p.y) + fabsf(row[2] * p.z) + fabsf(row[3]));
+    }
+    h.pi = MakeP3i(mk(q[0], q[1], q[2]), mk(qe[0], qe[1], qe[2]));
+    float wp = (m[12] * p.x + m[13] * p.y) + (m[14] * p.z + m[15]);
+    if (wp != 1) {  // Point3fi / wp (util/math.h:1028-1036); renderFromInstance is normally exactly affine
+        float *lo = &h.pi.lo.x, *hi = &h.pi.hi.x;
+        for (int r = 0; r < 3; ++r) {
+            float a = lo[r], b = hi[r];
+            lo[r] = wp > 0 ? NextDown(a / wp) : NextDown(b / wp);
+            hi[r] = wp > 0 ? NextUp(b / wp) : NextUp(a / wp);
+        }
+    }
+    auto nrm = [&](V3 n) {  // normals go through the inverse transpose
+        return mk(mi[0] * n.x + mi[4] * n.y + mi[8] * n.z, mi[1] * n.x + mi[5] * n.y + mi[9] * n.z,
+                  mi[2] * n.x + mi[6] * n.y + mi[10] * n.z);
+    };
+    auto vec = [&](V3 v) {
+        return mk(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z,
+                  m[8] * v.x + m[9] * v.y + m[10] * v.z);
+    };
+    h.n = Normalize(nrm(h.n));
+    h.wo = Normalize(vec(h.wo));
+    h.dpdus = vec(h.dpdus);
+    h.ns = FaceForward(Normalize(nrm(h.ns)), h.n);
+}
+
 // ------------------------------------------------------------------ area lights on triangles
 struct LightCtx {  // LightSampleContext (lights.h:83-101)
     P3i pi;

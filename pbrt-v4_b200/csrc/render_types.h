@@ -95,6 +95,7 @@ struct RenderSceneDev {
     const LightDev *lights;
     const MeshAttrDev *meshes;
     const void *prims;           // PrimSlot[] of the geometry scene
+    const void *instances;       // InstanceDev[] of the geometry scene (null if none)
     uint32_t nSpectra, nMaterials, nLights, nMeshes;
 };
 

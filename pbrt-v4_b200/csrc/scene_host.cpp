@@ -89,11 +89,6 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
     out.nMeshes = desc->n_meshes;
     for (uint32_t i = 0; i < desc->n_instances; ++i) {
         const b200pt_instance &in = desc->instances[i];
-        const float *r3 = in.instance_from_render + 12, *f3 = in.render_from_instance + 12;
-        if (r3[0] != 0 || r3[1] != 0 || r3[2] != 0 || r3[3] != 1 || f3[0] != 0 || f3[1] != 0 || f3[2] != 0 || f3[3] != 1) {
-            err = "instance transforms must be affine (last row 0 0 0 1)";
-            return B200PT_ERR_INVALID;
-        }
         if (!objMeshes.count(int32_t(in.object)) || int32_t(in.object) < 0) {
             err = "instance of an undefined object";
             return B200PT_ERR_INVALID;
@@ -198,6 +193,9 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                       z = (corner & 4) ? ob.hi[2] : ob.lo[2];
                 float pt[3];
                 for (int r = 0; r < 3; ++r) pt[r] = m[4 * r] * x + m[4 * r + 1] * y + m[4 * r + 2] * z + m[4 * r + 3];
+                float wp = m[12] * x + m[13] * y + m[14] * z + m[15];
+                if (wp != 1)
+                    for (int r = 0; r < 3; ++r) pt[r] = pt[r] / wp;
                 for (int c = 0; c < 3; ++c) {
                     bb.lo[c] = std::min(bb.lo[c], pt[c]);
                     bb.hi[c] = std::max(bb.hi[c], pt[c]);
@@ -317,8 +315,8 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             }
             InstanceDev d;
             std::memset(&d, 0, sizeof d);
-            std::memcpy(d.mInv, in.instance_from_render, 48);
-            std::memcpy(d.m, in.render_from_instance, 48);
+            std::memcpy(d.mInv, in.instance_from_render, 64);
+            std::memcpy(d.m, in.render_from_instance, 64);
             const Node32 &root = out.nodes[out.treeRoot[it->second]];
             std::memcpy(d.rootBox, root.bmin, 12);
             std::memcpy(d.rootBox + 3, root.bmax, 12);

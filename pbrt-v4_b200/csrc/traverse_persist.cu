@@ -205,8 +205,9 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                     push(left - 1, __float_as_int(tMax));
                     push(kReturn | (slot + 1), 0);
                     const float4 *mi = reinterpret_cast<const float4 *>(in->mInv);
-                    float4 r0 = __ldg(mi), r1 = __ldg(mi + 1), r2 = __ldg(mi + 2);
-                    float mInv[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
+                    float4 r0 = __ldg(mi), r1 = __ldg(mi + 1), r2 = __ldg(mi + 2), r3 = __ldg(mi + 3);
+                    float mInv[16] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w,
+                                      r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
                     float o2[3], d2[3], tMax2;
                     InstanceRay(mInv, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, tMax, o2, d2, tMax2);
                     RaySetup(r, o2[0], o2[1], o2[2], d2[0], d2[1], d2[2]);

@@ -16,12 +16,23 @@ class RenderScene:
         self.d = d
         nv, nt = d["mesh_nverts"].astype(np.int64), d["mesh_ntris"].astype(np.int64)
         vo, to = np.concatenate([[0], np.cumsum(nv)]), np.concatenate([[0], np.cumsum(nt)])
-        self.geometry = scenes.Scene([scenes.Mesh(d["P"][vo[i]:vo[i + 1]], d["indices"][to[i]:to[i + 1]])
-                                      for i in range(len(nv))])
+        obj = d["mesh_object"] if "mesh_object" in d else np.full(len(nv), -1, np.int32)
+        meshes = [scenes.Mesh(d["P"][vo[i]:vo[i + 1]], d["indices"][to[i]:to[i + 1]], object=int(obj[i]))
+                  for i in range(len(nv))]
+        insts = []
+        if "instance_object" in d:
+            insts = [scenes.Instance(int(o), m, mi)
+                     for o, m, mi in zip(d["instance_object"], d["instance_m"], d["instance_minv"])]
+        self.geometry = scenes.Scene(meshes, insts)
         self.bvh = None
         if "bvh_nodes" in d:
-            nodes = np.ascontiguousarray(d["bvh_nodes"]).view(capi.NODE32_DTYPE).reshape(-1)
-            self.bvh = [(-1, nodes, d["bvh_prims"])]
+            def nodes(a):
+                return np.ascontiguousarray(a).view(capi.NODE32_DTYPE).reshape(-1)
+            self.bvh = [(-1, nodes(d["bvh_nodes"]), d["bvh_prims"])]
+            k = 0
+            while f"obj_bvh_nodes_{k}" in d:
+                self.bvh.append((k, nodes(d[f"obj_bvh_nodes_{k}"]), d[f"obj_bvh_prims_{k}"]))
+                k += 1
 
     @classmethod
     def load(cls, path):
@@ -97,9 +108,13 @@ def scene_desc(geometry, bvh, keep):
             barr[k] = capi.BVH2(int(obj), nodes.shape[0], prims.shape[0], nodes.ctypes.data,
                                 prims.ctypes.data_as(C.POINTER(C.c_uint32)))
         nb = len(bvh)
-    insts = (capi.Instance * 1)()
+    insts = (capi.Instance * max(1, len(geometry.instances)))()
+    for k, i in enumerate(geometry.instances):
+        insts[k].object = int(i.object)
+        insts[k].render_from_instance[:] = [float(x) for x in i.render_from_instance.reshape(-1)]
+        insts[k].instance_from_render[:] = [float(x) for x in i.instance_from_render.reshape(-1)]
     keep += [meshes, barr, insts]
-    return capi.SceneDesc(len(geometry.meshes), meshes, 0, insts, nb, barr, 0)
+    return capi.SceneDesc(len(geometry.meshes), meshes, len(geometry.instances), insts, nb, barr, 0)
 
 
 class B200Renderer:

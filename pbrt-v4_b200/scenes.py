@@ -309,7 +309,7 @@ MATERIALS = {
 
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
-                 boxes=(None, None), regularize=False):
+                 boxes=(None, None), regularize=False, instanced=False):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -326,7 +326,18 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
         f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false',
         'WorldBegin',
     ]
+    if instanced:
+        # the two boxes become ONE object definition (a unit cube) placed twice (config 3's mechanism):
+        # ObjectBegin/ObjectInstance -> TransformedPrimitive over a per-object BVH (scene.cpp:1523-1575)
+        unit = _box((-0.5, -0.5, -0.5), (0.5, 0.5, 0.5))
+        lines += ['AttributeBegin', '  ' + MATERIALS.get(boxes[0], boxes[0] or f'Material "diffuse" "rgb reflectance" [{white[0]} {white[1]} {white[2]}]'),
+                  '  ObjectBegin "cube"', '    ' + _mesh_pbrt(unit), '  ObjectEnd', 'AttributeEnd']
+        for (tx, ty, tz, sx, sy, sz, rot) in [(0.3, 0.3, 0.65, 0.3, 0.6, 0.3, 17.0), (0.7, 0.15, 0.35, 0.3, 0.3, 0.3, -18.0)]:
+            lines += ['AttributeBegin', f'  Translate {tx} {ty} {tz}', f'  Rotate {rot} 0 1 0', f'  Scale {sx} {sy} {sz}',
+                      '  ObjectInstance "cube"', 'AttributeEnd']
     for k, (m, c) in enumerate(zip(sc.meshes, colours)):
+        if instanced and k in (6, 7):
+            continue
         lines.append('AttributeBegin')
         if override.get(k):
             lines.append('  ' + MATERIALS.get(override[k], override[k]))

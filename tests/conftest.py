@@ -37,7 +37,8 @@ def hostcheck_bin():
     src = [os.path.join(ROOT, "tests", "native", "hostcheck.cpp"),
            os.path.join(ROOT, "pbrt-v4_b200", "csrc", "scene_host.cpp"),
            os.path.join(ROOT, "pbrt-v4_b200", "csrc", "bvh2_build.cpp")]
-    deps = src + [os.path.join(ROOT, "pbrt-v4_b200", "csrc", h) for h in ("isect.h", "scene_host.h", "bvh2.h")]
+    deps = src + [os.path.join(ROOT, "pbrt-v4_b200", "csrc", h) for h in ("isect.h", "instance.h", "scene_host.h", "bvh2.h")] \
+        + [os.path.join(ROOT, "tests", "native", "trace_host.h")]
     if not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in deps):
         os.makedirs(os.path.dirname(out), exist_ok=True)
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-march=x86-64-v3", "-o", out] + src)
@@ -70,7 +71,8 @@ def rendercheck(P):
     out = os.path.join(ROOT, "tests", "native", "_build", "librendercheck.so")
     src = [os.path.join(ROOT, "tests", "native", "rendercheck.cpp")] + \
           [os.path.join(csrc, f) for f in ("scene_host.cpp", "bvh2_build.cpp", "render_host.cpp")]
-    deps = src + [os.path.join(csrc, h) for h in os.listdir(csrc) if h.endswith(".h")]
+    deps = src + [os.path.join(csrc, h) for h in os.listdir(csrc) if h.endswith(".h")] \
+        + [os.path.join(ROOT, "tests", "native", "trace_host.h")]
     if not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in deps):
         os.makedirs(os.path.dirname(out), exist_ok=True)
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-march=x86-64-v3", "-shared",

@@ -54,6 +54,7 @@ RENDER_CASES = {
     "cornell_metal_r64_s16": dict(res=64, spp=16, maxdepth=5, boxes=("conductor_rough", "conductor_smooth")),
     "cornell_metal2_r48_s8": dict(res=48, spp=8, maxdepth=4, boxes=("conductor_reflectance", "dielectric_rough"),
                                   regularize=True),
+    "cornell_instanced_r64_s16": dict(res=64, spp=16, maxdepth=5, instanced=True, boxes=("conductor_rough", None)),
     "cornell_glass_r64_s16": dict(res=64, spp=16, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass")),
 }
 # Cases whose gate is the Monte-Carlo noise floor (rRMSE(ours, ref) <= 1.25 x rRMSE(ref seed s,

@@ -12,81 +12,9 @@
 #include <string>
 #include <vector>
 
-#include "../../pbrt-v4_b200/csrc/instance.h"
-#include "../../pbrt-v4_b200/csrc/isect.h"
-#include "../../pbrt-v4_b200/csrc/scene_host.h"
+#include "trace_host.h"
 
 using namespace b200pt;
-
-struct Best {
-    int slot = -1, inst = -1;  // inst: index into hs.instances, -1 = world geometry
-    float b1 = 0, b2 = 0;
-};
-
-// PairNode walk with the {ref, tMin} stack and the pop-time `tMin < tMax` re-check, as
-// traverse_persist.cu does it; an instance leaf recurses with the transformed ray (the device kernel
-// keeps the way back on its stack instead - same visits, same arithmetic).
-static bool TracePairs(const HostScene &hs, int rootRef, const float *rootBox, const float *o, const float *d,
-                       float &tMax, bool any, Best &best, int curInst, bool dbg) {
-    RayCtx r;
-    RaySetup(r, o[0], o[1], o[2], d[0], d[1], d[2]);
-    struct E { int ref; float t; };
-    E stack[128];
-    int sp = 0, cur = 0;
-    bool done = false;
-    auto popNext = [&]() {
-        done = true;
-        while (sp > 0) {
-            E e = stack[--sp];
-            if (e.t < tMax) { cur = e.ref; done = false; break; }
-        }
-    };
-    // a one-primitive object has no BVH and no box (scene.cpp:1551): rootBox == nullptr
-    if (!rootBox || SlabTest(r, rootBox, rootBox + 3, tMax)) cur = rootRef; else done = true;
-    while (!done) {
-        if (cur >= 0) {
-            const PairNode &pn = hs.pairs[cur];
-            float t0, t1;
-            bool h0 = SlabCore(r, pn.box0, pn.box0 + 3, t0);
-            bool h1 = SlabCore(r, pn.box1, pn.box1 + 3, t1);
-            if (dbg)
-                fprintf(stderr, "pair %d: h0 %d t0 %g ref0 %d | h1 %d t1 %g ref1 %d | tMax %.9g\n", cur, h0, t0, pn.ref0, h1, t1, pn.ref1, tMax);
-            bool neg = r.neg[pn.axis] != 0;
-            int nearRef = neg ? pn.ref1 : pn.ref0, farRef = neg ? pn.ref0 : pn.ref1;
-            float tNear = neg ? t1 : t0, tFar = neg ? t0 : t1;
-            bool hNear = (neg ? h1 : h0) && (tNear < tMax), hFar = neg ? h0 : h1;
-            if (hFar) stack[sp++] = E{farRef, tFar};
-            if (hNear) cur = nearRef;
-            else popNext();
-        } else {
-            int slot = ~cur, cnt = int(hs.prims[slot].flags);
-            for (int k = 0; k < cnt; ++k, ++slot) {
-                const PrimSlot &s = hs.prims[slot];
-                if (s.mesh == kInstanceTag) {
-                    const InstanceDev &in = hs.instances[s.tri];
-                    float o2[3], d2[3], tMax2;
-                    InstanceRay(in.mInv, o[0], o[1], o[2], d[0], d[1], d[2], tMax, o2, d2, tMax2);
-                    Best sub;
-                    bool h = TracePairs(hs, in.rootRef, in.rootRef < 0 ? nullptr : in.rootBox, o2, d2, tMax2, any, sub,
-                                        int(s.tri), dbg);
-                    if (any && h) return true;
-                    if (!any && sub.slot >= 0) {  // the parent goes on with tMax = the object's t, not shifted back
-                        tMax = tMax2;
-                        best = sub;
-                    }
-                    continue;
-                }
-                float t, b0, b1, b2;
-                if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
-                    if (any) return true;
-                    tMax = t; best.slot = slot; best.inst = curInst; best.b1 = b1; best.b2 = b2;
-                }
-            }
-            popNext();
-        }
-    }
-    return any ? false : best.slot >= 0;
-}
 
 // the reference's own loop shape over the LinearBVHNode layout (cpu/aggregates.cpp:529-579)
 static bool TraceNodes(const HostScene &hs, int root, bool testRoot, const float *o, const float *d, float &tMax,

@@ -11,65 +11,22 @@
 #include "../../pbrt-v4_b200/csrc/render_core.h"
 #include "../../pbrt-v4_b200/csrc/render_host.h"
 #include "../../pbrt-v4_b200/csrc/scene_host.h"
+#include "trace_host.h"
 
 using namespace b200pt;
 
 namespace {
 
-struct E {
-    int ref;
-    float t;
-};
-
-// closest hit -> internal record {slot, t, b0, b1, b2, 0}; any = occlusion only
+// closest hit -> internal record {slot, t, b0, b1, b2, instance + 1}; any = occlusion only
 bool Trace(const HostScene &hs, V3 o, V3 d, float tMax, bool any, uint32_t hit[6]) {
-    RayCtx r;
-    RaySetup(r, o.x, o.y, o.z, d.x, d.y, d.z);
-    E stack[128];
-    int sp = 0, cur = 0, best = -1;
-    float bb0 = 0, bb1 = 0, bb2 = 0;
-    bool done = false;
-    auto popNext = [&]() {
-        done = true;
-        while (sp > 0) {
-            E e = stack[--sp];
-            if (e.t < tMax) {
-                cur = e.ref;
-                done = false;
-                break;
-            }
-        }
-    };
-    if (SlabTest(r, hs.bounds, hs.bounds + 3, tMax)) cur = hs.rootRef; else done = true;
-    while (!done) {
-        if (cur >= 0) {
-            const PairNode &pn = hs.pairs[cur];
-            float t0, t1;
-            bool h0 = SlabCore(r, pn.box0, pn.box0 + 3, t0), h1 = SlabCore(r, pn.box1, pn.box1 + 3, t1);
-            bool neg = r.neg[pn.axis] != 0;
-            int nearRef = neg ? pn.ref1 : pn.ref0, farRef = neg ? pn.ref0 : pn.ref1;
-            float tNear = neg ? t1 : t0, tFar = neg ? t0 : t1;
-            bool hNear = (neg ? h1 : h0) && (tNear < tMax), hFar = neg ? h0 : h1;
-            if (hFar) stack[sp++] = E{farRef, tFar};
-            if (hNear) cur = nearRef; else popNext();
-        } else {
-            int slot = ~cur, cnt = int(hs.prims[slot].flags);
-            for (int k = 0; k < cnt; ++k, ++slot) {
-                const PrimSlot &s = hs.prims[slot];
-                float t, b0, b1, b2;
-                if (TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
-                    if (any) return true;
-                    tMax = t; best = slot; bb0 = b0; bb1 = b1; bb2 = b2;
-                }
-            }
-            popNext();
-        }
-    }
-    if (any) return false;
-    if (best < 0) { hit[0] = kMissTag; return false; }
-    hit[0] = uint32_t(best);
-    memcpy(&hit[1], &tMax, 4); memcpy(&hit[2], &bb0, 4); memcpy(&hit[3], &bb1, 4); memcpy(&hit[4], &bb2, 4);
-    hit[5] = 0;
+    float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+    Best best;
+    bool h = TracePairs(hs, hs.rootRef, hs.bounds, oo, dd, tMax, any, best, -1, false);
+    if (any) return h;
+    if (best.slot < 0) { hit[0] = kMissTag; return false; }
+    hit[0] = uint32_t(best.slot);
+    memcpy(&hit[1], &tMax, 4); memcpy(&hit[2], &best.b0, 4); memcpy(&hit[3], &best.b1, 4); memcpy(&hit[4], &best.b2, 4);
+    hit[5] = uint32_t(best.inst + 1);
     return true;
 }
 
@@ -112,6 +69,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.lights = rh.lights.data();
     rs.meshes = rh.meshes.data();
     rs.prims = hs.prims.data();
+    rs.instances = hs.instances.data();
     const int W = rh.width, H = rh.height;
     if (nThreads < 1) nThreads = 1;
     std::vector<std::thread> pool;
@@ -158,6 +116,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.lights = rh.lights.data();
     rs.meshes = rh.meshes.data();
     rs.prims = hs.prims.data();
+    rs.instances = hs.instances.data();
     int full = rs.integrator.maxDepth;
     for (int d = 0; d <= full; ++d) {
         rs.integrator.maxDepth = d;
