@@ -311,6 +311,10 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
         ShadeKernel<MAT_DIELECTRIC><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
         ++*launches;
     }
+    if (matMask & 8u) {
+        ShadeKernel<MAT_COATED_DIFFUSE><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
+        ++*launches;
+    }
     return cudaGetLastError();
 }
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {

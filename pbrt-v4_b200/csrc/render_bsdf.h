@@ -161,9 +161,13 @@ struct BsdfSample {
 // Scalar part of an f(wo, wi) evaluation; the spectral factor is applied per wavelength by
 // BsdfSpectral().  kind: 0 zero, 1 constant*`scale` (same for all k), 2 diffuse R_k*scale,
 // 3 conductor ((D*F_k)*G)/denom with F_k = FrComplex(cosF, eta_k, k_k), 4 specular conductor F_k/denom.
+// 5 coated diffuse: sum_a poly[a] * R_k^a (the random walk of LayeredBxDF only ever multiplies the
+// throughput by scalars and by the diffuse base's R_k, so its value is a polynomial in R_k).
+constexpr int kLayerPoly = 14;
 struct BsdfEval {
     int kind;
     float scale, D, G, denom, cosF;
+    float poly[kLayerPoly];
 };
 
 // One surface's BxDF, as GetBxDF leaves it (materials.h): the spectra stay in their tables and are
@@ -173,9 +177,117 @@ struct Bsdf {
     uint32_t type;      // MaterialType
     TRDist tr;          // conductor, dielectric
     float eta;          // dielectric: eta(lambda[0])
-    int32_t specA;      // diffuse: reflectance; conductor: eta, or reflectance when specB < 0
+    int32_t specA;      // diffuse, coated diffuse: reflectance; conductor: eta, or reflectance when specB < 0
     int32_t specB;      // conductor: k
+    // coated diffuse (LayeredBxDF<DielectricBxDF, DiffuseBxDF, true>, bxdfs.h:565-1041)
+    float thickness, rMax;  // rMax = max_k R_k at this path's wavelengths
+    int maxDepth, nSamples;
+    int32_t layerSeed;      // Options::seed, hashed into the random walks' generators
 };
+
+// ---- DielectricBxDF with explicit TransportMode and BxDFReflTransFlags (bxdfs.cpp:77-255): the coated
+// materials call their top interface with Importance mode and with one of the two lobes masked out.
+enum : uint32_t { SF_REFLECTION = 1, SF_TRANSMISSION = 2, SF_ALL = 3 };
+
+B2_HD float DielF(float eta, const TRDist &tr, V3 wo, V3 wi, bool radiance) {
+    if (eta == 1 || TRSmooth(tr)) return 0;
+    float cosTheta_o = CosTheta(wo), cosTheta_i = CosTheta(wi);
+    bool reflect = cosTheta_i * cosTheta_o > 0;
+    float etap = 1;
+    if (!reflect) etap = cosTheta_o > 0 ? eta : (1 / eta);
+    V3 wm = wi * etap + wo;
+    if (cosTheta_i == 0 || cosTheta_o == 0 || LengthSquared(wm) == 0) return 0;
+    wm = FaceForward(Normalize(wm), mk(0, 0, 1));
+    if (Dot(wm, wi) * cosTheta_i < 0 || Dot(wm, wo) * cosTheta_o < 0) return 0;
+    float F = FrDielectric(Dot(wo, wm), eta);
+    if (reflect) return TR_D(tr, wm) * TR_G(tr, wo, wi) * F / fabsf(4 * cosTheta_i * cosTheta_o);
+    float denom = SqrF(Dot(wi, wm) + Dot(wo, wm) / etap) * cosTheta_i * cosTheta_o;
+    float ft = TR_D(tr, wm) * (1 - F) * TR_G(tr, wo, wi) * fabsf(Dot(wi, wm) * Dot(wo, wm) / denom);
+    if (radiance) ft /= SqrF(etap);
+    return ft;
+}
+
+B2_HD float DielPDF(float eta, const TRDist &tr, V3 wo, V3 wi, uint32_t sflags) {
+    if (eta == 1 || TRSmooth(tr)) return 0;
+    float cosTheta_o = CosTheta(wo), cosTheta_i = CosTheta(wi);
+    bool reflect = cosTheta_i * cosTheta_o > 0;
+    float etap = 1;
+    if (!reflect) etap = cosTheta_o > 0 ? eta : (1 / eta);
+    V3 wm = wi * etap + wo;
+    if (cosTheta_i == 0 || cosTheta_o == 0 || LengthSquared(wm) == 0) return 0;
+    wm = FaceForward(Normalize(wm), mk(0, 0, 1));
+    if (Dot(wm, wi) * cosTheta_i < 0 || Dot(wm, wo) * cosTheta_o < 0) return 0;
+    float R = FrDielectric(Dot(wo, wm), eta), T = 1 - R;
+    float pr = (sflags & SF_REFLECTION) ? R : 0, pt = (sflags & SF_TRANSMISSION) ? T : 0;
+    if (pr == 0 && pt == 0) return 0;
+    if (reflect) return TR_PDF(tr, wo, wm) / (4 * AbsDot(wo, wm)) * pr / (pr + pt);
+    float denom = SqrF(Dot(wi, wm) + Dot(wo, wm) / etap);
+    float dwm_dwi = AbsDot(wi, wm) / denom;
+    return TR_PDF(tr, wo, wm) * dwm_dwi * pt / (pr + pt);
+}
+
+// returns the sample; `f` is the (wavelength-independent) BSDF value
+B2_HD BsdfSample DielSample(float eta, const TRDist &tr, V3 wo, float uc, float u0, float u1, bool radiance,
+                            uint32_t sflags, float &f) {
+    BsdfSample s{false, mk(0, 0, 0), 0, 0, 1, false};
+    f = 0;
+    if (eta == 1 || TRSmooth(tr)) {
+        float R = FrDielectric(CosTheta(wo), eta), T = 1 - R;
+        float pr = (sflags & SF_REFLECTION) ? R : 0, pt = (sflags & SF_TRANSMISSION) ? T : 0;
+        if (pr == 0 && pt == 0) return s;
+        if (uc < pr / (pr + pt)) {
+            V3 wi = mk(-wo.x, -wo.y, wo.z);
+            f = R / AbsCosTheta(wi);
+            s.wi = wi;
+            s.pdf = pr / (pr + pt);
+            s.flags = BX_SPECULAR | BX_REFLECTION;
+            s.ok = true;
+            return s;
+        }
+        V3 wi;
+        float etap;
+        if (!Refract(wo, mk(0, 0, 1), eta, &etap, &wi)) return s;
+        float ft = T / AbsCosTheta(wi);
+        if (radiance) ft /= SqrF(etap);
+        f = ft;
+        s.wi = wi;
+        s.pdf = pt / (pr + pt);
+        s.flags = BX_SPECULAR | BX_TRANSMISSION;
+        s.eta = etap;
+        s.ok = true;
+        return s;
+    }
+    V3 wm = TR_Sample_wm(tr, wo, u0, u1);
+    float R = FrDielectric(Dot(wo, wm), eta), T = 1 - R;
+    float pr = (sflags & SF_REFLECTION) ? R : 0, pt = (sflags & SF_TRANSMISSION) ? T : 0;
+    if (pr == 0 && pt == 0) return s;
+    if (uc < pr / (pr + pt)) {
+        V3 wi = Reflect(wo, wm);
+        if (!SameHemisphere(wo, wi)) return s;
+        s.pdf = TR_PDF(tr, wo, wm) / (4 * AbsDot(wo, wm)) * pr / (pr + pt);
+        f = TR_D(tr, wm) * TR_G(tr, wo, wi) * R / (4 * CosTheta(wi) * CosTheta(wo));
+        s.wi = wi;
+        s.flags = BX_GLOSSY | BX_REFLECTION;
+        s.ok = true;
+        return s;
+    }
+    float etap;
+    V3 wi = mk(0, 0, 0);
+    bool tir = !Refract(wo, wm, eta, &etap, &wi);
+    if (tir || SameHemisphere(wo, wi) || wi.z == 0) return s;
+    float denom = SqrF(Dot(wi, wm) + Dot(wo, wm) / etap);
+    float dwm_dwi = AbsDot(wi, wm) / denom;
+    s.pdf = TR_PDF(tr, wo, wm) * dwm_dwi * pt / (pr + pt);
+    float ft = T * TR_D(tr, wm) * TR_G(tr, wo, wi) *
+               fabsf(Dot(wi, wm) * Dot(wo, wm) / (CosTheta(wi) * CosTheta(wo) * denom));
+    if (radiance) ft /= SqrF(etap);
+    f = ft;
+    s.wi = wi;
+    s.flags = BX_GLOSSY | BX_TRANSMISSION;
+    s.eta = etap;
+    s.ok = true;
+    return s;
+}
 
 B2_HD uint32_t BsdfFlags(const Bsdf &b) {
     switch (b.type) {
@@ -185,14 +297,28 @@ B2_HD uint32_t BsdfFlags(const Bsdf &b) {
         uint32_t f = (b.eta == 1) ? BX_TRANSMISSION : (BX_REFLECTION | BX_TRANSMISSION);
         return f | (TRSmooth(b.tr) ? BX_SPECULAR : BX_GLOSSY);
     }
+    case MAT_COATED_DIFFUSE: {  // LayeredBxDF::Flags (bxdfs.h:589-606): dielectric top, diffuse bottom, no medium
+        uint32_t f = BX_REFLECTION;
+        bool topSpecular = TRSmooth(b.tr);
+        if (topSpecular) f |= BX_SPECULAR;
+        if (b.rMax != 0) f |= BX_DIFFUSE;
+        else if (!topSpecular) f |= BX_GLOSSY;
+        return f;
+    }
     }
     return 0;
 }
 B2_HD void BsdfRegularize(Bsdf &b) {
-    if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC) TRRegularize(b.tr);
+    if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC || b.type == MAT_COATED_DIFFUSE) TRRegularize(b.tr);
 }
 
-B2_HD BsdfEval ZeroEval() { return BsdfEval{0, 0, 0, 0, 1, 0}; }
+B2_HD BsdfEval ZeroEval() {
+    BsdfEval e;
+    e.kind = 0;
+    e.scale = e.D = e.G = e.cosF = 0;
+    e.denom = 1;
+    return e;
+}
 
 // scalar part of BxDF::f(wo, wi, Radiance)
 B2_HD BsdfEval BsdfF(const Bsdf &b, V3 wo, V3 wi) {
@@ -219,24 +345,10 @@ B2_HD BsdfEval BsdfF(const Bsdf &b, V3 wo, V3 wi) {
         return e;
     }
     if (b.type == MAT_DIELECTRIC) {  // DielectricBxDF::f (bxdfs.cpp:167-205)
-        if (b.eta == 1 || TRSmooth(b.tr)) return e;
-        float cosTheta_o = CosTheta(wo), cosTheta_i = CosTheta(wi);
-        bool reflect = cosTheta_i * cosTheta_o > 0;
-        float etap = 1;
-        if (!reflect) etap = cosTheta_o > 0 ? b.eta : (1 / b.eta);
-        V3 wm = wi * etap + wo;
-        if (cosTheta_i == 0 || cosTheta_o == 0 || LengthSquared(wm) == 0) return e;
-        wm = FaceForward(Normalize(wm), mk(0, 0, 1));
-        if (Dot(wm, wi) * cosTheta_i < 0 || Dot(wm, wo) * cosTheta_o < 0) return e;
-        float F = FrDielectric(Dot(wo, wm), b.eta);
-        e.kind = 1;
-        if (reflect) {
-            e.scale = TR_D(b.tr, wm) * TR_G(b.tr, wo, wi) * F / fabsf(4 * cosTheta_i * cosTheta_o);
-        } else {
-            float denom = SqrF(Dot(wi, wm) + Dot(wo, wm) / etap) * cosTheta_i * cosTheta_o;
-            float ft = TR_D(b.tr, wm) * (1 - F) * TR_G(b.tr, wo, wi) * fabsf(Dot(wi, wm) * Dot(wo, wm) / denom);
-            ft /= SqrF(etap);
-            e.scale = ft;
+        float f = DielF(b.eta, b.tr, wo, wi, true);
+        if (f != 0) {
+            e.kind = 1;
+            e.scale = f;
         }
         return e;
     }
@@ -257,24 +369,7 @@ B2_HD float BsdfPDF(const Bsdf &b, V3 wo, V3 wi) {
         wm = FaceForward(Normalize(wm), mk(0, 0, 1));
         return TR_PDF(b.tr, wo, wm) / (4 * AbsDot(wo, wm));
     }
-    if (b.type == MAT_DIELECTRIC) {  // bxdfs.cpp:207-255
-        if (b.eta == 1 || TRSmooth(b.tr)) return 0;
-        float cosTheta_o = CosTheta(wo), cosTheta_i = CosTheta(wi);
-        bool reflect = cosTheta_i * cosTheta_o > 0;
-        float etap = 1;
-        if (!reflect) etap = cosTheta_o > 0 ? b.eta : (1 / b.eta);
-        V3 wm = wi * etap + wo;
-        if (cosTheta_i == 0 || cosTheta_o == 0 || LengthSquared(wm) == 0) return 0;
-        wm = FaceForward(Normalize(wm), mk(0, 0, 1));
-        if (Dot(wm, wi) * cosTheta_i < 0 || Dot(wm, wo) * cosTheta_o < 0) return 0;
-        float R = FrDielectric(Dot(wo, wm), b.eta), T = 1 - R;
-        float pr = R, pt = T;
-        if (pr == 0 && pt == 0) return 0;
-        if (reflect) return TR_PDF(b.tr, wo, wm) / (4 * AbsDot(wo, wm)) * pr / (pr + pt);
-        float denom = SqrF(Dot(wi, wm) + Dot(wo, wm) / etap);
-        float dwm_dwi = AbsDot(wi, wm) / denom;
-        return TR_PDF(b.tr, wo, wm) * dwm_dwi * pt / (pr + pt);
-    }
+    if (b.type == MAT_DIELECTRIC) return DielPDF(b.eta, b.tr, wo, wi, SF_ALL);  // bxdfs.cpp:207-255
     return 0;
 }
 
@@ -325,62 +420,7 @@ B2_HD BsdfSample BsdfSampleF(const Bsdf &b, V3 wo, float uc, float u0, float u1,
     }
     if (b.type == MAT_DIELECTRIC) {  // bxdfs.cpp:77-165
         ev.kind = 1;
-        if (b.eta == 1 || TRSmooth(b.tr)) {
-            float R = FrDielectric(CosTheta(wo), b.eta), T = 1 - R;
-            float pr = R, pt = T;
-            if (pr == 0 && pt == 0) return s;
-            if (uc < pr / (pr + pt)) {
-                V3 wi = mk(-wo.x, -wo.y, wo.z);
-                ev.scale = R / AbsCosTheta(wi);
-                s.wi = wi;
-                s.pdf = pr / (pr + pt);
-                s.flags = BX_SPECULAR | BX_REFLECTION;
-                s.ok = true;
-                return s;
-            }
-            V3 wi;
-            float etap;
-            if (!Refract(wo, mk(0, 0, 1), b.eta, &etap, &wi)) return s;
-            float ft = T / AbsCosTheta(wi);
-            ft /= SqrF(etap);
-            ev.scale = ft;
-            s.wi = wi;
-            s.pdf = pt / (pr + pt);
-            s.flags = BX_SPECULAR | BX_TRANSMISSION;
-            s.eta = etap;
-            s.ok = true;
-            return s;
-        }
-        V3 wm = TR_Sample_wm(b.tr, wo, u0, u1);
-        float R = FrDielectric(Dot(wo, wm), b.eta), T = 1 - R;
-        float pr = R, pt = T;
-        if (pr == 0 && pt == 0) return s;
-        if (uc < pr / (pr + pt)) {
-            V3 wi = Reflect(wo, wm);
-            if (!SameHemisphere(wo, wi)) return s;
-            s.pdf = TR_PDF(b.tr, wo, wm) / (4 * AbsDot(wo, wm)) * pr / (pr + pt);
-            ev.scale = TR_D(b.tr, wm) * TR_G(b.tr, wo, wi) * R / (4 * CosTheta(wi) * CosTheta(wo));
-            s.wi = wi;
-            s.flags = BX_GLOSSY | BX_REFLECTION;
-            s.ok = true;
-            return s;
-        }
-        float etap;
-        V3 wi = mk(0, 0, 0);
-        bool tir = !Refract(wo, wm, b.eta, &etap, &wi);
-        if (tir || SameHemisphere(wo, wi) || wi.z == 0) return s;
-        float denom = SqrF(Dot(wi, wm) + Dot(wo, wm) / etap);
-        float dwm_dwi = AbsDot(wi, wm) / denom;
-        s.pdf = TR_PDF(b.tr, wo, wm) * dwm_dwi * pt / (pr + pt);
-        float ft = T * TR_D(b.tr, wm) * TR_G(b.tr, wo, wi) *
-                   fabsf(Dot(wi, wm) * Dot(wo, wm) / (CosTheta(wi) * CosTheta(wo) * denom));
-        ft /= SqrF(etap);
-        ev.scale = ft;
-        s.wi = wi;
-        s.flags = BX_GLOSSY | BX_TRANSMISSION;
-        s.eta = etap;
-        s.ok = true;
-        return s;
+        return DielSample(b.eta, b.tr, wo, uc, u0, u1, true, SF_ALL, ev.scale);
     }
     return s;
 }

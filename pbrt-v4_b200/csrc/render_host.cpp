@@ -92,8 +92,19 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
             if (m.spectrum[0] >= 0 ? m.spectrum[1] < 0 : m.spectrum[2] < 0)
                 return bad("conductor needs eta and k, or reflectance");
             break;
+        case B200PT_MAT_COATED_DIFFUSE: {  // reflectance, albedo (must be black: no medium between the layers), eta
+            if (!specOk(m.spectrum[0]) || !specOk(m.spectrum[2]) || !opt(m.spectrum[1]))
+                return bad("material spectrum index out of range");
+            if (m.spectrum[1] >= 0)
+                for (int k = 0; k < B200PT_SPECTRUM_SAMPLES; ++k)
+                    if (d->spectra[m.spectrum[1]].values[k] != 0)
+                        return bad("coateddiffuse with a scattering medium between the layers (albedo != 0) is not implemented");
+            if (m.params[6] < 1 || m.params[6] > 24 || m.params[7] < 1)
+                return bad("coateddiffuse maxdepth must be 1..24 and nsamples >= 1");
+            break;
+        }
         default:
-            return bad("unsupported material type (diffuse, conductor, dielectric are implemented)");
+            return bad("unsupported material type");
         }
         out.materials[i].type = m.type;
         std::memcpy(out.materials[i].spectrum, m.spectrum, 16);

@@ -14,6 +14,7 @@
 // kernel ~20 K instructions and instruction-fetch bound (profiles/r01_render_v2_*).
 #pragma once
 #include "render_bsdf.h"
+#include "render_layered.h"
 
 namespace b200pt {
 
@@ -98,7 +99,11 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
     b.eta = 1;
     b.specA = mat.spectrum[0];
     b.specB = -1;
-    if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC) {
+    b.thickness = 0;
+    b.rMax = 0;
+    b.maxDepth = b.nSamples = 0;
+    b.layerSeed = 0;  // Options::seed (options.h), 0 unless the host was started with --seed
+    if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC || b.type == MAT_COATED_DIFFUSE) {
         float ur = mat.params[0], vr = mat.params[1];
         if (mat.params[2] != 0) {  // remaproughness: RoughnessToAlpha = sqrt
             ur = sqrtf(ur);
@@ -121,7 +126,33 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
         if (e == 0) e = 1;
         b.eta = e;
     }
+    if (b.type == MAT_COATED_DIFFUSE) {  // CoatedDiffuseMaterial::GetBxDF (materials.cpp:301-329)
+        float e = SpectrumAt(rs.spectra[mat.spectrum[2]], lambda0);
+        if (mat.params[3] == 0) p.flags |= PF_TERMINATED_SECONDARY;
+        if (e == 0) e = 1;
+        b.eta = e;
+        b.thickness = fmaxf(mat.params[4], 1.17549435e-38f);
+        b.maxDepth = (int)mat.params[6];
+        b.nSamples = (int)mat.params[7];
+        float rm = 0;
+        LambdaIter li(p.lambdaU);
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k, li.Next()) rm = fmaxf(rm, Clampf(SpectrumAt(rs.spectra[b.specA], li.lam), 0, 1));
+        b.rMax = rm;
+    }
     return b;
+}
+
+// the four BxDF entry points with the layered model added (it needs its own header)
+B2_HD BsdfEval EvalF(const Bsdf &b, V3 wo, V3 wi) {
+    return b.type == MAT_COATED_DIFFUSE ? CoatedF(b, wo, wi, b.layerSeed) : BsdfF(b, wo, wi);
+}
+B2_HD float EvalPDF(const Bsdf &b, V3 wo, V3 wi) {
+    return b.type == MAT_COATED_DIFFUSE ? CoatedPDF(b, wo, wi, b.layerSeed) : BsdfPDF(b, wo, wi);
+}
+B2_HD BsdfSample EvalSample(const Bsdf &b, V3 wo, float uc, float u0, float u1, BsdfEval &ev) {
+    return b.type == MAT_COATED_DIFFUSE ? CoatedSample(b, wo, uc, u0, u1, b.layerSeed, ev)
+                                        : BsdfSampleF(b, wo, uc, u0, u1, ev);
 }
 
 // f_k: the per-wavelength factor applied to the scalar evaluation `e` (see BsdfEval)
@@ -129,6 +160,12 @@ B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval
     switch (e.kind) {
     case 1: return e.scale;
     case 2: return Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, 1) * e.scale;  // DiffuseMaterial clamps R
+    case 5: {  // coated diffuse: polynomial in R_k (render_layered.h)
+        float R = Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, 1);
+        float v = e.poly[kLayerPoly - 1];
+        for (int a = kLayerPoly - 2; a >= 0; --a) v = v * R + e.poly[a];
+        return v;
+    }
     case 3:
     case 4: {
         float etaK, kK;
@@ -208,6 +245,8 @@ B2_SPECTRAL_LOOP
     }
     const MaterialDev mat = rs.materials[mesh.material];
     Bsdf bsdf = MakeBsdf<MAT>(rs, mat, LambdaIter(p.lambdaU).lam, p);
+    // regularize first: it can turn a specular lobe glossy, which changes Flags() (cpu/integrators.cpp:714-718)
+    if (rs.integrator.regularize && (p.flags & PF_ANY_NONSPECULAR)) BsdfRegularize(bsdf);
     uint32_t bflags = BsdfFlags(bsdf);
     if (bsdf.type == MAT_DIFFUSE) {  // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
         bool anyR = false;
@@ -216,7 +255,6 @@ B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k, li.Next()) anyR |= Clampf(SpectrumAt(rs.spectra[bsdf.specA], li.lam), 0, 1) != 0;
         if (!anyR) bflags = 0;
     }
-    if (rs.integrator.regularize && (p.flags & PF_ANY_NONSPECULAR)) BsdfRegularize(bsdf);
     // BSDF shading frame: Frame::FromXZ(Normalize(dpdus), ns) (bsdf.h:24-25)
     V3 fx = Normalize(si.dpdus), fz = si.ns, fy = Cross(fz, fx);
     V3 woL = mk(Dot(wo, fx), Dot(wo, fy), Dot(wo, fz));
@@ -272,11 +310,11 @@ B2_SPECTRAL_LOOP
                         atten = fmaxf((1.0f - (light.tanFalloffEnd * tan_a)) * light.normalizeFalloffEnd, 0.0f);
                     }
                     V3 wiL = mk(Dot(wi, fx), Dot(wi, fy), Dot(wi, fz));
-                    BsdfEval ev = (woLd.z == 0) ? ZeroEval() : BsdfF(bsdf, woLd, wiL);  // BSDF::f (bsdf.h:37-43)
+                    BsdfEval ev = (woLd.z == 0) ? ZeroEval() : EvalF(bsdf, woLd, wiL);  // BSDF::f (bsdf.h:37-43)
                     if (ev.kind != 0) {
                         float absCos = AbsDotN(si.ns, wi);
                         float p_l = pmf * ss.pdf;
-                        float p_b = woLd.z == 0 ? 0.f : BsdfPDF(bsdf, woLd, wiL);
+                        float p_b = woLd.z == 0 ? 0.f : EvalPDF(bsdf, woLd, wiL);
                         float w_l = PowerHeuristic(p_l, p_b);
                         const SpectrumTable &sp = rs.spectra[light.spectrum];
                         bool anyL = false, anyF = false;
@@ -310,7 +348,7 @@ B2_SPECTRAL_LOOP
         return;
     }
     BsdfEval ev;
-    BsdfSample bs = BsdfSampleF(bsdf, woL, uc, u0, u1, ev);
+    BsdfSample bs = EvalSample(bsdf, woL, uc, u0, u1, ev);
     if (!bs.ok || bs.pdf == 0 || bs.wi.z == 0) {
         KillPath(p);
         return;
@@ -335,7 +373,7 @@ B2_SPECTRAL_LOOP
         KillPath(p);
         return;
     }
-    p.pB = bs.pdfIsProportional ? BsdfPDF(bsdf, woL, bs.wi) : bs.pdf;
+    p.pB = bs.pdfIsProportional ? EvalPDF(bsdf, woL, bs.wi) : bs.pdf;
     bool specular = (bs.flags & BX_SPECULAR) != 0;
     p.flags = specular ? (p.flags | PF_SPECULAR) : ((p.flags & ~PF_SPECULAR) | PF_ANY_NONSPECULAR);
     if (bs.flags & BX_TRANSMISSION) p.etaScale *= SqrF(bs.eta);

@@ -55,6 +55,7 @@ RENDER_CASES = {
     "cornell_metal2_r48_s8": dict(res=48, spp=8, maxdepth=4, boxes=("conductor_reflectance", "dielectric_rough"),
                                   regularize=True),
     "cornell_instanced_r64_s16": dict(res=64, spp=16, maxdepth=5, instanced=True, boxes=("conductor_rough", None)),
+    "cornell_coated_r64_s16": dict(res=64, spp=16, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough")),
     "cornell_glass_r64_s16": dict(res=64, spp=16, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass")),
 }
 # Cases whose gate is the Monte-Carlo noise floor (rRMSE(ours, ref) <= 1.25 x rRMSE(ref seed s,
@@ -65,7 +66,9 @@ RENDER_CASES = {
 # For these a second reference image at seed + 1 is stored (<name>_ref2.npy).
 # (metal2 follows the reference path for path on the CPU check, which shares glibc's sinf/cosf with the
 # reference; on the GPU the last-bit differences of CUDA's sinf/cosf flip a few such roulette tests.)
-NOISE_GATED = {"cornell_glass_r64_s16", "cornell_metal2_r48_s8"}
+# (coated: the layered BxDF's random walk is carried as a polynomial in R_k here, csrc/render_layered.h, so its
+# internal roulette tests see max_k beta_k with different rounding: most walks are the reference's, a few are not.)
+NOISE_GATED = {"cornell_glass_r64_s16", "cornell_metal2_r48_s8", "cornell_coated_r64_s16"}
 # scene tables only (no image): BASELINE.json configs[0] at full size, for bench.py and the
 # full-size GPU test, which render the reference image on the spot with oracle/_ref/pbrt_ref
 TABLE_CASES = {

@@ -45,6 +45,18 @@ def noise_gate(img, ref, ref2):
     return rrmse(img, ref) <= 1.25 * floor and abs(img.mean() - ref.mean()) <= 0.01 * ref.mean(), floor
 
 
+def test_golden_image_coated(P, rendercheck):
+    """CoatedDiffuse (LayeredBxDF random walks; smooth and rough coats).  Noise gate, and the measured
+    distance stays a small fraction of the floor because nearly all walks are the reference's."""
+    name = "cornell_coated_r64_s16"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref, ref2 = (np.load(os.path.join(GOLD, name + s)) for s in ("_ref.npy", "_ref2.npy"))
+    img = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
+    ok, floor = noise_gate(img, ref, ref2)
+    assert ok, (rrmse(img, ref), floor)
+    assert rrmse(img, ref) <= 0.05 * floor
+
+
 def test_golden_image_smooth_glass(P, rendercheck):
     """Smooth dielectrics (one with a wavelength-dependent index: TerminateSecondary).  Gate = noise floor
     (tests/golden/make_golden.py NOISE_GATED says why); most paths still follow the reference's, so the
