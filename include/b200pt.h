@@ -185,8 +185,10 @@ typedef struct b200pt_material {
     float params[8];
 } b200pt_material;
 
-/* DiffuseAreaLight on one triangle (lights.h:407-500) + its PowerLightSampler alias-table bin
+/* DiffuseAreaLight on one triangle (lights.h:407-500) or a UniformInfiniteLight (lights.h:512-554:
+ * spectrum + scale only; mesh/tri unused) + its PowerLightSampler alias-table bin
  * (lightsamplers.cpp:76-96, util/sampling.cpp:562-617).  Order = the host's `lights` vector. */
+enum { B200PT_LIGHT_AREA_TRIANGLE = 0, B200PT_LIGHT_UNIFORM_INFINITE = 1 };
 typedef struct b200pt_light {
     uint32_t mesh, tri;
     int32_t spectrum; /* Lemit */
@@ -195,6 +197,7 @@ typedef struct b200pt_light {
     float cos_falloff_end, tan_falloff_end, normalize_falloff_end;
     float alias_q, alias_p;
     int32_t alias;
+    uint32_t type;
 } b200pt_light;
 
 typedef struct b200pt_mesh_attr {
@@ -224,12 +227,22 @@ typedef struct b200pt_render_desc {
     /* integrator: path (cpu/integrators.cpp:629-805) */
     int32_t max_depth;
     uint32_t regularize;
-    uint32_t light_sampler; /* 0 uniform, 1 power */
+    uint32_t light_sampler; /* 0 uniform, 1 power, 2 bvh */
     uint32_t n_spectra, n_materials, n_lights, n_meshes;
     const b200pt_spectrum *spectra;
     const b200pt_material *materials;
     const b200pt_light *lights;
     const b200pt_mesh_attr *meshes; /* one per mesh of the geometry scene */
+    /* BVHLightSampler (lightsamplers.h:266-375), built by the host (lightsamplers.cpp:109-232).
+     * light_bvh_nodes: n_light_bvh_nodes x 32 B = eight u32 {w.x | w.y << 16 (OctahedralVector), phi,
+     * qCosTheta_o | qCosTheta_e << 15 | twoSided << 30, qb[0][0] | qb[0][1] << 16, qb[0][2] | qb[1][0] << 16,
+     * qb[1][1] | qb[1][2] << 16, childOrLightIndex | isLeaf << 31, 0} (LightBVHNode, lightsamplers.h:203-264);
+     * light_bvh_bounds = allLightBounds; light_bit_trails[n_lights] = lightToBitTrail, 0xFFFFFFFF for a
+     * light that is not in the tree.  Needed only when light_sampler == 2. */
+    uint32_t n_light_bvh_nodes;
+    float light_bvh_bounds[6];
+    const void *light_bvh_nodes;
+    const uint32_t *light_bit_trails;
 } b200pt_render_desc;
 
 typedef struct b200pt_render b200pt_render;

@@ -151,6 +151,10 @@ int main(int argc, char **argv) {
     Camera camera = scene.GetCamera();
     Film film = camera.GetFilm();
     Sampler sampler = scene.GetSampler();
+    {  // Integrator constructor (cpu/integrators.h:66-73): infinite lights learn the scene's bounding sphere
+        Bounds3f sceneBounds = accel ? accel.Bounds() : Bounds3f();
+        for (auto &light : lights) light.Preprocess(sceneBounds);
+    }
 
     // ---- debug mode: `dumpscene_ref scene.pbrt --path x y sampleIndex` prints, for one pixel sample, the
     // radiance the reference's PathIntegrator::Li returns when maxDepth is cut at 0, 1, 2, ... (the
@@ -483,18 +487,74 @@ int main(int argc, char **argv) {
     std::vector<float> lightF;
     std::map<const void *, int> lemitId;
     for (size_t i = 0; i < lights.size(); ++i) {
+        const auto &bin = pls.aliasTable.bins[i];
+        if (const UniformInfiniteLight *ul = lights[i].CastOrNullptr<UniformInfiniteLight>()) {
+            if (!lemitId.count(ul->Lemit)) lemitId[ul->Lemit] = pool.add(ul->Lemit, 0);
+            lightI.insert(lightI.end(), {-1, -1, lemitId[ul->Lemit], 0, bin.alias, -1, 1});
+            lightF.insert(lightF.end(), {ul->scale, 0.f, 0.f, 0.f, bin.q, bin.p});
+            continue;
+        }
         const DiffuseAreaLight *al = lights[i].CastOrNullptr<DiffuseAreaLight>();
-        if (!al) die("only diffuse area lights are dumped so far");
+        if (!al) die("only diffuse area lights and uniform infinite lights are dumped so far");
         if (al->image) die("image area lights are not dumped");
         if (!lemitId.count(al->Lemit)) lemitId[al->Lemit] = pool.add(al->Lemit, 0);
         int m = lightMeshTri[2 * i], tri = lightMeshTri[2 * i + 1];
         if (m < 0) die("area light without a triangle in the aggregate");
-        const auto &bin = pls.aliasTable.bins[i];
-        lightI.insert(lightI.end(), {m, tri, lemitId[al->Lemit], al->twoSided ? 1 : 0, bin.alias, meshAttr[3 * m + 2]});
+        lightI.insert(lightI.end(), {m, tri, lemitId[al->Lemit], al->twoSided ? 1 : 0, bin.alias, meshAttr[3 * m + 2], 0});
         lightF.insert(lightF.end(), {al->scale, al->cosFalloffEnd, al->tanFalloffEnd, al->normalize_falloffEnd, bin.q, bin.p});
     }
-    w.i32("lights_i", {uint32_t(lights.size()), 6}, lightI);
+    w.i32("lights_i", {uint32_t(lights.size()), 7}, lightI);
     w.f32("lights_f", {uint32_t(lights.size()), 6}, lightF);
+
+    // ---- the light BVH (lightsamplers.cpp:109-232), node fields as include/b200pt.h lists them
+    if (lsId == 2) {
+        BVHLightSampler bls(pstd::span<const Light>(lights.data(), lights.size()), Allocator());
+        std::vector<uint32_t> nodes;
+        for (const LightBVHNode &nd : bls.nodes) {
+            const CompactLightBounds &cb = nd.lightBounds;
+            uint32_t phiBits;
+            memcpy(&phiBits, &cb.phi, 4);
+            nodes.insert(nodes.end(),
+                         {uint32_t(cb.w.x) | uint32_t(cb.w.y) << 16, phiBits,
+                          uint32_t(cb.qCosTheta_o) | uint32_t(cb.qCosTheta_e) << 15 | uint32_t(cb.twoSided) << 30,
+                          uint32_t(cb.qb[0][0]) | uint32_t(cb.qb[0][1]) << 16,
+                          uint32_t(cb.qb[0][2]) | uint32_t(cb.qb[1][0]) << 16,
+                          uint32_t(cb.qb[1][1]) | uint32_t(cb.qb[1][2]) << 16,
+                          uint32_t(nd.childOrLightIndex) | uint32_t(nd.isLeaf) << 31, 0u});
+        }
+        std::vector<uint32_t> trails(lights.size(), 0xFFFFFFFFu);
+        for (size_t i = 0; i < lights.size(); ++i)
+            if (bls.lightToBitTrail.HasKey(lights[i])) trails[i] = bls.lightToBitTrail[lights[i]];
+        const Bounds3f &ab = bls.allLightBounds;
+        w.u32("lightbvh_nodes", {uint32_t(bls.nodes.size()), 8}, nodes);
+        w.u32("lightbvh_trails", {uint32_t(lights.size())}, trails);
+        w.f32("lightbvh_bounds", {6}, {ab.pMin.x, ab.pMin.y, ab.pMin.z, ab.pMax.x, ab.pMax.y, ab.pMax.z});
+        // known answers of BVHLightSampler::Sample / PMF at random reference points (p, ns, u); ns = 0 for a
+        // third of them (points in media).  Checked bit for bit by tests/test_render_core.py.
+        const int nProbe = 768;
+        RNG rng(7, 11);
+        Bounds3f sb = accel.Bounds();
+        std::vector<float> pin, pout;
+        std::vector<int32_t> pidx;
+        for (int i = 0; i < nProbe; ++i) {
+            Point3f p = sb.Lerp(Point3f(rng.Uniform<Float>() * 1.2f - .1f, rng.Uniform<Float>() * 1.2f - .1f,
+                                        rng.Uniform<Float>() * 1.2f - .1f));
+            Normal3f n(0, 0, 0);
+            if (i % 3) n = Normal3f(SampleUniformSphere(Point2f(rng.Uniform<Float>(), rng.Uniform<Float>())));
+            Float u = rng.Uniform<Float>();
+            LightSampleContext ctx(Point3fi(p), n, n);
+            pstd::optional<SampledLight> sl = bls.Sample(ctx, u);
+            int li = sl ? lightIndex[sl->light.ptr()] : -1;
+            // PMF of the sampled light, or of light (i mod nLights) when nothing was sampled
+            int lq = li >= 0 ? li : int(i % lights.size());
+            pin.insert(pin.end(), {p.x, p.y, p.z, n.x, n.y, n.z, u});
+            pidx.insert(pidx.end(), {li, lq});
+            pout.insert(pout.end(), {sl ? sl->p : 0.f, bls.PMF(ctx, lights[lq])});
+        }
+        w.f32("lightbvh_probe_in", {uint32_t(nProbe), 7}, pin);
+        w.i32("lightbvh_probe_light", {uint32_t(nProbe), 2}, pidx);
+        w.f32("lightbvh_probe_pmf", {uint32_t(nProbe), 2}, pout);
+    }
 
     w.f32("spectra_values", {uint32_t(pool.interp.size()), 311}, pool.values);
     w.u32("spectra_interp", {uint32_t(pool.interp.size())}, pool.interp);

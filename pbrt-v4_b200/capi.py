@@ -131,7 +131,7 @@ class Light(C.Structure):
     _fields_ = [("mesh", C.c_uint32), ("tri", C.c_uint32), ("spectrum", C.c_int32), ("scale", C.c_float),
                 ("two_sided", C.c_uint32), ("cos_falloff_end", C.c_float), ("tan_falloff_end", C.c_float),
                 ("normalize_falloff_end", C.c_float), ("alias_q", C.c_float), ("alias_p", C.c_float),
-                ("alias", C.c_int32)]
+                ("alias", C.c_int32), ("type", C.c_uint32)]
 
 
 class MeshAttr(C.Structure):
@@ -148,7 +148,9 @@ class RenderDesc(C.Structure):
                 ("randomize", C.c_uint32), ("max_depth", C.c_int32), ("regularize", C.c_uint32),
                 ("light_sampler", C.c_uint32), ("n_spectra", C.c_uint32), ("n_materials", C.c_uint32),
                 ("n_lights", C.c_uint32), ("n_meshes", C.c_uint32), ("spectra", C.POINTER(Spectrum)),
-                ("materials", C.POINTER(Material)), ("lights", C.POINTER(Light)), ("meshes", C.POINTER(MeshAttr))]
+                ("materials", C.POINTER(Material)), ("lights", C.POINTER(Light)), ("meshes", C.POINTER(MeshAttr)),
+                ("n_light_bvh_nodes", C.c_uint32), ("light_bvh_bounds", C.c_float * 6),
+                ("light_bvh_nodes", C.c_void_p), ("light_bit_trails", C.POINTER(C.c_uint32))]
 
 
 class RenderStats(C.Structure):

@@ -160,7 +160,20 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
     int *counts = pb.counts + kCountStride * depth;
     if (t >= counts[0]) return;
     uint32_t slot = pb.hits[6ll * t];
-    if (slot == kMissTag) return;  // escaped: no infinite lights yet, the path ends
+    if (slot == kMissTag) {  // escaped: infinite lights add their radiance, the path ends
+        if (rs.nInfiniteLights) {
+            struct {
+                const PassBuffers &pb;
+                int path;
+                __device__ float Beta(int k) const { return pb.beta[(long long)k * pb.n + path]; }
+                __device__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
+            } io{pb, pb.rayPath[depth & 1][t]};
+            const long long n = pb.n;
+            uint32_t flags = (uint32_t)pb.ints[3 * n + io.path];
+            EscapedRadiance(rs, pb.scalars[io.path], depth == 0 || (flags & PF_SPECULAR), pb.scalars[2 * n + io.path], io);
+        }
+        return;
+    }
     const PrimSlot *ps = reinterpret_cast<const PrimSlot *>(rs.prims) + slot;
     int material = rs.meshes[ps->mesh].material;
     uint32_t type = material >= 0 ? rs.materials[material].type : 0u;  // null material: any queue ends the path

@@ -22,6 +22,7 @@ struct b200pt_render {
     RenderHost host;
     RenderSceneDev dev{};
     void *dSpectra = nullptr, *dMaterials = nullptr, *dLights = nullptr, *dMeshes = nullptr;
+    void *dLightBvh = nullptr, *dBitTrails = nullptr, *dInfinite = nullptr;
     double *dFilm = nullptr;
     float *dImage = nullptr;
     void *dPaths = nullptr;
@@ -59,6 +60,9 @@ int b200pt_render_destroy(b200pt_render *r) {
     cudaFree(r->dMaterials);
     cudaFree(r->dLights);
     cudaFree(r->dMeshes);
+    cudaFree(r->dLightBvh);
+    cudaFree(r->dBitTrails);
+    cudaFree(r->dInfinite);
     cudaFree(r->dFilm);
     cudaFree(r->dImage);
     cudaFree(r->dPaths);
@@ -90,7 +94,10 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         return fail(B200PT_ERR_CUDA);
     }
     if ((rc = Upload(ctx, r->host.spectra, &r->dSpectra)) || (rc = Upload(ctx, r->host.materials, &r->dMaterials)) ||
-        (rc = Upload(ctx, r->host.lights, &r->dLights)) || (rc = Upload(ctx, r->host.meshes, &r->dMeshes)))
+        (rc = Upload(ctx, r->host.lights, &r->dLights)) || (rc = Upload(ctx, r->host.meshes, &r->dMeshes)) ||
+        (rc = Upload(ctx, r->host.lightBvhNodes, &r->dLightBvh)) ||
+        (rc = Upload(ctx, r->host.lightBitTrails, &r->dBitTrails)) ||
+        (rc = Upload(ctx, r->host.infiniteLights, &r->dInfinite)))
         return fail(rc);
     r->nPixels = r->host.width * r->host.height;
     r->dev = r->host.rs;
@@ -98,6 +105,9 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     r->dev.materials = (const MaterialDev *)r->dMaterials;
     r->dev.lights = (const LightDev *)r->dLights;
     r->dev.meshes = (const MeshAttrDev *)r->dMeshes;
+    r->dev.lightBvhNodes = r->dLightBvh;
+    r->dev.lightBitTrails = (const uint32_t *)r->dBitTrails;
+    r->dev.infiniteLights = (const int32_t *)r->dInfinite;
     r->dev.prims = scene->dev.prims;
     r->dev.instances = scene->dev.instances;
     for (const MaterialDev &m : r->host.materials) r->matMask |= 1u << m.type;

@@ -28,7 +28,9 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     if (d->camera_type != 0) return bad("unsupported camera type");
     if (d->film_type != 0) return bad("unsupported film type");
     if (d->sampler_type != 0) return bad("unsupported sampler type");
-    if (d->light_sampler > 1) return bad("unsupported light sampler (uniform and power are implemented)");
+    if (d->light_sampler > 2) return bad("unsupported light sampler (uniform, power and bvh are implemented)");
+    if (d->light_sampler == 2 && d->n_lights && (!d->light_bit_trails || (d->n_light_bvh_nodes && !d->light_bvh_nodes)))
+        return bad("the bvh light sampler needs light_bvh_nodes and light_bit_trails");
     if (d->n_meshes != nSceneMeshes) return bad("mesh attribute count differs from the geometry scene");
     if ((d->n_spectra && !d->spectra) || (d->n_materials && !d->materials) || (d->n_lights && !d->lights) ||
         (d->n_meshes && !d->meshes))
@@ -124,13 +126,19 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     out.lights.resize(d->n_lights);
     for (uint32_t i = 0; i < d->n_lights; ++i) {
         const b200pt_light &l = d->lights[i];
-        auto it = slotOf.find((uint64_t(l.mesh) << 32) | l.tri);
-        if (it == slotOf.end()) return bad("light refers to a triangle that is not in the scene");
+        if (l.type > B200PT_LIGHT_UNIFORM_INFINITE) return bad("unsupported light type");
+        uint32_t slot = 0;
+        if (l.type == B200PT_LIGHT_AREA_TRIANGLE) {
+            auto it = slotOf.find((uint64_t(l.mesh) << 32) | l.tri);
+            if (it == slotOf.end()) return bad("light refers to a triangle that is not in the scene");
+            slot = it->second;
+        } else
+            out.infiniteLights.push_back(int32_t(i));
         if (!specOk(l.spectrum)) return bad("light spectrum index out of range");
         if (l.alias >= int32_t(d->n_lights)) return bad("alias index out of range");
         LightDev &o = out.lights[i];
-        o.type = 0;
-        o.slot = it->second;
+        o.type = l.type;
+        o.slot = slot;
         o.spectrum = l.spectrum;
         o.scale = l.scale;
         o.twoSided = l.two_sided;
@@ -142,6 +150,21 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         o.alias = l.alias;
         o.flipNormal = l.mesh < d->n_meshes ? d->meshes[l.mesh].flip_normal : 0;
     }
+    rs.nLightBvhNodes = 0;
+    if (d->light_sampler == 2) {
+        const uint32_t *nodes = static_cast<const uint32_t *>(d->light_bvh_nodes);
+        for (uint32_t i = 0; i < d->n_light_bvh_nodes; ++i) {
+            uint32_t link = nodes[8 * i + 6];
+            if (link >> 31 ? (link & 0x7FFFFFFFu) >= d->n_lights
+                           : ((link & 0x7FFFFFFFu) >= d->n_light_bvh_nodes || i + 1 >= d->n_light_bvh_nodes))
+                return bad("light BVH node refers outside its tables");
+        }
+        out.lightBvhNodes.assign(nodes, nodes + 8 * size_t(d->n_light_bvh_nodes));
+        out.lightBitTrails.assign(d->light_bit_trails, d->light_bit_trails + d->n_lights);
+        rs.nLightBvhNodes = d->n_light_bvh_nodes;
+        std::memcpy(rs.lightBvhBounds, d->light_bvh_bounds, 24);
+    }
+    rs.nInfiniteLights = uint32_t(out.infiniteLights.size());
     rs.nSpectra = d->n_spectra;
     rs.nMaterials = d->n_materials;
     rs.nLights = d->n_lights;

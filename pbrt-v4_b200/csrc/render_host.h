@@ -16,6 +16,9 @@ struct RenderHost {
     std::vector<MaterialDev> materials;
     std::vector<LightDev> lights;
     std::vector<MeshAttrDev> meshes;
+    std::vector<uint32_t> lightBvhNodes;   // 8 per node
+    std::vector<uint32_t> lightBitTrails;  // per light
+    std::vector<int32_t> infiniteLights;   // light indices
     int width = 0, height = 0;
 };
 

@@ -15,6 +15,7 @@
 #pragma once
 #include "render_bsdf.h"
 #include "render_layered.h"
+#include "render_lightbvh.h"
 
 namespace b200pt {
 
@@ -184,13 +185,32 @@ B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval
     return 0.f;
 }
 
+// Escaped ray: every infinite light adds beta * Le, MIS-weighted against light sampling unless the ray
+// left the camera or a specular bounce (cpu/integrators.cpp:645-662).  UniformInfiniteLight::PDF_Li is 0
+// under allowIncompletePDF (lights.cpp:998-1003), so the weight is PowerHeuristic(p_b, 0).
+template <class IO>
+B2_HD void EscapedRadiance(const RenderSceneDev &rs, float lambdaU, bool unweighted, float pB, IO &io) {
+    for (uint32_t i = 0; i < rs.nInfiniteLights; ++i) {
+        const LightDev &light = rs.lights[rs.infiniteLights[i]];
+        const SpectrumTable &sp = rs.spectra[light.spectrum];
+        float w = unweighted ? 1.f : PowerHeuristic(pB, 0.f);
+        LambdaIter li(lambdaU);
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+            float Le = light.scale * SpectrumAt(sp, li.lam);
+            io.AddL(k, unweighted ? io.Beta(k) * Le : io.Beta(k) * w * Le);
+        }
+    }
+}
+
 // One path vertex.  `hit` is the internal record {slot, t, b0, b1, b2} of the closest-hit kernel for
 // p.ray.  IO: AddL(k, v) adds to the path's radiance; ShadowBegin() / SetLd(k, v) / ShadowEnd(valid,
 // o, d, tMax) record a light sample whose visibility is still unknown; Beta(k) / SetBeta(k, v) are the
 // path throughput.
 template <class IO, int MAT = -1>
 B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit[6], IO &io) {
-    if (hit[0] == kMissTag) {  // no infinite lights yet: an escaped ray adds nothing (cpu/integrators.cpp:645-662)
+    if (hit[0] == kMissTag) {  // escaped ray (cpu/integrators.cpp:645-662); the kernels do this in ClassifyKernel
+        if (rs.nInfiniteLights) EscapedRadiance(rs, p.lambdaU, p.depth == 0 || (p.flags & PF_SPECULAR), p.pB, io);
         KillPath(p);
         return;
     }
@@ -225,6 +245,8 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
             if (!(p.depth == 0 || (p.flags & PF_SPECULAR))) {
                 float pmf = al.aliasP;  // PowerLightSampler::PMF (lightsamplers.h:78-82)
                 if (rs.integrator.lightSampler == 0) pmf = 1.f / rs.nLights;
+                if (rs.integrator.lightSampler == 2)
+                    pmf = LightBvhPMF(rs, Mid(p.prev.pi), p.prev.ns, mesh.lightFirst + (int)tv.tri);
                 float p_l = pmf * TrianglePDF(tv, p.prev, p.rayD, al.flipNormal != 0);
                 w = PowerHeuristic(p.pB, p_l);
             }
@@ -289,15 +311,23 @@ B2_SPECTRAL_LOOP
             if (rs.integrator.lightSampler == 0) {
                 lidx = (int)fminf(uL * nl, (float)(nl - 1));
                 pmf = 1.f / nl;
+            } else if (rs.integrator.lightSampler == 2) {
+                lidx = LightBvhSample(rs, Mid(ctx.pi), ctx.ns, uL, &pmf);
             } else {
                 int offset = (int)fminf(uL * nl, (float)(nl - 1));
                 float up = fminf(uL * nl - offset, kOneMinusEps);
                 lidx = (up < rs.lights[offset].aliasQ) ? offset : rs.lights[offset].alias;
                 pmf = rs.lights[lidx].aliasP;
             }
-            const LightDev light = rs.lights[lidx];
-            TriVerts lt = LoadTri(rs.prims, light.slot);
-            ShapeSampleOut ss = SampleTriangleSolidAngle(lt, ctx, uLight0, uLight1, light.flipNormal != 0);
+            // no light chosen, or a UniformInfiniteLight: its SampleLi gives nothing under
+            // allowIncompletePDF (lights.cpp:986-990); it is found by BSDF sampling alone
+            const LightDev light = rs.lights[lidx < 0 ? 0 : lidx];
+            ShapeSampleOut ss;
+            ss.ok = false;
+            if (lidx >= 0 && light.type == 0) {
+                TriVerts lt = LoadTri(rs.prims, light.slot);
+                ss = SampleTriangleSolidAngle(lt, ctx, uLight0, uLight1, light.flipNormal != 0);
+            }
             V3 cp = Mid(ctx.pi);
             if (ss.ok && ss.pdf != 0 && LengthSquared(Mid(ss.pi) - cp) != 0) {
                 V3 wi = Normalize(Mid(ss.pi) - cp);

@@ -33,7 +33,7 @@ struct MaterialDev {
 
 // DiffuseAreaLight on one triangle (lights.h:410-470) + its alias-table bin (util/sampling.h:804).
 struct LightDev {
-    uint32_t type;       // 0 = diffuse area light on a triangle
+    uint32_t type;       // 0 = diffuse area light on a triangle, 1 = uniform infinite light
     uint32_t slot;       // PrimSlot of its triangle
     int32_t spectrum;    // Lemit
     float scale;
@@ -82,7 +82,7 @@ struct SamplerDev {
 struct IntegratorDev {
     int32_t maxDepth;
     uint32_t regularize;
-    uint32_t lightSampler;       // 0 uniform, 1 power
+    uint32_t lightSampler;       // 0 uniform, 1 power, 2 bvh
 };
 
 struct RenderSceneDev {
@@ -97,6 +97,12 @@ struct RenderSceneDev {
     const void *prims;           // PrimSlot[] of the geometry scene
     const void *instances;       // InstanceDev[] of the geometry scene (null if none)
     uint32_t nSpectra, nMaterials, nLights, nMeshes;
+    // BVHLightSampler (render_lightbvh.h) and the infinite lights (indices into lights)
+    const void *lightBvhNodes;
+    const uint32_t *lightBitTrails;
+    const int32_t *infiniteLights;
+    uint32_t nLightBvhNodes, nInfiniteLights;
+    float lightBvhBounds[6];
 };
 
 // Per-path state, structure of arrays over `n` paths of a pass.  Spectral arrays are [k][path].

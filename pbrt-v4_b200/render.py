@@ -79,8 +79,10 @@ class RenderScene:
         lights = (capi.Light * max(nl, 1))()
         for i in range(nl):
             li, lf = d["lights_i"][i], d["lights_f"][i]
-            lights[i] = capi.Light(int(li[0]), int(li[1]), int(li[2]), float(lf[0]), int(li[3]), float(lf[1]),
-                                   float(lf[2]), float(lf[3]), float(lf[4]), float(lf[5]), int(li[4]))
+            ltype = int(li[6]) if len(li) > 6 else 0  # 1: uniform infinite light (no triangle)
+            lights[i] = capi.Light(max(int(li[0]), 0), max(int(li[1]), 0), int(li[2]), float(lf[0]), int(li[3]),
+                                   float(lf[1]), float(lf[2]), float(lf[3]), float(lf[4]), float(lf[5]), int(li[4]),
+                                   ltype)
         meshes = (capi.MeshAttr * max(nme, 1))()
         for i in range(nme):
             a = d["mesh_attr"][i]
@@ -88,6 +90,14 @@ class RenderScene:
         r.n_spectra, r.n_materials, r.n_lights, r.n_meshes = ns, nm, nl, nme
         r.spectra, r.materials, r.lights, r.meshes = spectra, mats, lights, meshes
         keep += [spectra, mats, lights, meshes]
+        if r.light_sampler == 2:  # BVHLightSampler tables
+            nodes = np.ascontiguousarray(d["lightbvh_nodes"], np.uint32)
+            trails = np.ascontiguousarray(d["lightbvh_trails"], np.uint32)
+            r.n_light_bvh_nodes = len(nodes)
+            r.light_bvh_bounds[:] = [float(x) for x in d["lightbvh_bounds"]]
+            r.light_bvh_nodes = nodes.ctypes.data
+            r.light_bit_trails = trails.ctypes.data_as(C.POINTER(C.c_uint32))
+            keep += [nodes, trails]
         return r
 
 

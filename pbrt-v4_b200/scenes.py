@@ -309,7 +309,7 @@ MATERIALS = {
 
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
-                 boxes=(None, None), regularize=False, instanced=False):
+                 boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -348,6 +348,26 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
             lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
         lines.append('  ' + _mesh_pbrt(m))
         lines.append('AttributeEnd')
+    if many_lights:
+        # config 3's "many-light" mechanism at test size: small one-sided emissive quads of varied power,
+        # position and orientation inside the box (what the light BVH's importance has to tell apart)
+        rng = np.random.default_rng(1234 + many_lights)
+        for _ in range(many_lights):
+            c = rng.uniform(0.08, 0.92, 3)
+            n = rng.normal(size=3)
+            n /= np.linalg.norm(n)
+            a = np.cross(n, [0.0, 1.0, 0.0] if abs(n[1]) < 0.9 else [1.0, 0.0, 0.0])
+            a /= np.linalg.norm(a)
+            b = np.cross(n, a)
+            h = rng.uniform(0.01, 0.03)
+            q = [c - h * a - h * b, c + h * a - h * b, c + h * a + h * b, c - h * a + h * b]
+            L = rng.uniform(0.5, 40.0) * rng.uniform(0.3, 1.0, 3)
+            pts = " ".join(f"{float(v):.7g}" for pt in q for v in pt)
+            lines += ['AttributeBegin', f'  AreaLightSource "diffuse" "rgb L" [{L[0]:.5g} {L[1]:.5g} {L[2]:.5g}]',
+                      '  Material "diffuse" "rgb reflectance" [0 0 0]',
+                      f'  Shape "trianglemesh" "point3 P" [{pts}] "integer indices" [0 1 2 0 2 3]', 'AttributeEnd']
+    if infinite is not None:
+        lines.append(f'LightSource "infinite" "rgb L" [{infinite[0]} {infinite[1]} {infinite[2]}]')
     with open(path, "w") as f:
         f.write("\n".join(lines) + "\n")
     return sc

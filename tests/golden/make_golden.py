@@ -55,6 +55,11 @@ RENDER_CASES = {
     "cornell_metal2_r48_s8": dict(res=48, spp=8, maxdepth=4, boxes=("conductor_reflectance", "dielectric_rough"),
                                   regularize=True),
     "cornell_instanced_r64_s16": dict(res=64, spp=16, maxdepth=5, instanced=True, boxes=("conductor_rough", None)),
+    # BVHLightSampler over 202 emitters (the "many-light" mechanism of configs[2]); with a uniform infinite light
+    "cornell_manylights_r64_s16": dict(res=64, spp=16, maxdepth=5, lightsampler="bvh", many_lights=200),
+    "cornell_infinite_r64_s16": dict(res=64, spp=16, maxdepth=5, lightsampler="bvh", many_lights=20,
+                                     infinite=(0.4, 0.5, 0.8)),
+    "cornell_infinite_power_r48_s8": dict(res=48, spp=8, maxdepth=4, lightsampler="power", infinite=(0.4, 0.5, 0.8)),
     "cornell_coated_r64_s16": dict(res=64, spp=16, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough")),
     "cornell_glass_r64_s16": dict(res=64, spp=16, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass")),
 }

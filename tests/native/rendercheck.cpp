@@ -68,6 +68,9 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.materials = rh.materials.data();
     rs.lights = rh.lights.data();
     rs.meshes = rh.meshes.data();
+    rs.lightBvhNodes = rh.lightBvhNodes.data();
+    rs.lightBitTrails = rh.lightBitTrails.data();
+    rs.infiniteLights = rh.infiniteLights.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     const int W = rh.width, H = rh.height;
@@ -115,6 +118,9 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.materials = rh.materials.data();
     rs.lights = rh.lights.data();
     rs.meshes = rh.meshes.data();
+    rs.lightBvhNodes = rh.lightBvhNodes.data();
+    rs.lightBitTrails = rh.lightBitTrails.data();
+    rs.infiniteLights = rh.infiniteLights.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     int full = rs.integrator.maxDepth;
@@ -151,6 +157,30 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
 }
 
 // ---- small probes for tests/test_render_core.py
+// BVHLightSampler::Sample at n reference points {p, ns, u}; PMF of light query[i] at the same point.
+extern "C" int rendercheck_lightbvh(const b200pt_scene_desc *sd, const b200pt_render_desc *rd, const float *in,
+                                    const int *query, int n, int *light, float *pmf) {
+    HostScene hs;
+    RenderHost rh;
+    std::string err;
+    int rc = AssembleScene(sd, hs, err);
+    if (rc == 0) rc = BuildRenderTables(rd, hs, sd->n_meshes, rh, err);
+    if (rc != 0) return rc;
+    RenderSceneDev rs = rh.rs;
+    rs.lights = rh.lights.data();
+    rs.lightBvhNodes = rh.lightBvhNodes.data();
+    rs.lightBitTrails = rh.lightBitTrails.data();
+    rs.infiniteLights = rh.infiniteLights.data();
+    for (int i = 0; i < n; ++i) {
+        const float *c = in + 7 * i;
+        float pm = 0.f;
+        light[i] = LightBvhSample(rs, mk(c[0], c[1], c[2]), mk(c[3], c[4], c[5]), c[6], &pm);
+        pmf[2 * i] = light[i] >= 0 ? pm : 0.f;
+        pmf[2 * i + 1] = LightBvhPMF(rs, mk(c[0], c[1], c[2]), mk(c[3], c[4], c[5]), query[i]);
+    }
+    return 0;
+}
+
 extern "C" uint32_t rendercheck_sobol_column(int dim, int j) { return b200pt::SobolColumn(dim, j); }
 extern "C" uint32_t rendercheck_sobol_dim1(uint64_t a) { return b200pt::SobolDim1(a); }
 extern "C" int rendercheck_permute(int p, int digit) { return b200pt::ZSobolPermute(p, digit); }

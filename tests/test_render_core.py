@@ -75,3 +75,38 @@ def test_nearest_spectrum_lookup_is_lround(P, rendercheck):
         off = int(np.floor(np.float64(x) + 0.5)) - 395  # lround: half away from zero, x > 0
         want = float(off) if 0 <= off < 311 else 0.0
         assert L.rendercheck_spectrum_at(C.byref(s), float(x)) == want, x
+
+
+import pytest
+
+
+@pytest.mark.parametrize("name", ["cornell_manylights_r64_s16", "cornell_infinite_r64_s16"])
+def test_light_bvh_sample_and_pmf_match_reference(P, rendercheck, name):
+    """BVHLightSampler::Sample / PMF (lightsamplers.h:266-358) at 768 random reference points against the
+    answers the reference gave when the fixture was dumped (oracle/dumpscene_ref.cpp): the light chosen and
+    both probabilities, bit for bit.  Then the properties the reference's own tests pin
+    (lightsamplers_test.cpp:24-352): Sample's probability is PMF(light) of the light it returned."""
+    rsc = P.RenderScene.load(os.path.join(ROOT, "tests", "golden", name + ".b2rs"))
+    d = rsc.d
+    keep = []
+    sd = P.render.scene_desc(rsc.geometry, None, keep)
+    rd = rsc.desc(keep)
+    L = _lib(rendercheck)
+    pin = np.ascontiguousarray(d["lightbvh_probe_in"], np.float32)
+    query = np.ascontiguousarray(d["lightbvh_probe_light"][:, 1], np.int32)
+    n = len(pin)
+    light = np.zeros(n, np.int32)
+    pmf = np.zeros((n, 2), np.float32)
+    rc = L.rendercheck_lightbvh(C.byref(sd), C.byref(rd), pin.ctypes.data_as(C.c_void_p),
+                                query.ctypes.data_as(C.c_void_p), n, light.ctypes.data_as(C.c_void_p),
+                                pmf.ctypes.data_as(C.c_void_p))
+    assert rc == 0
+    assert np.array_equal(light, d["lightbvh_probe_light"][:, 0])
+    assert np.array_equal(pmf.view(np.uint32), np.ascontiguousarray(d["lightbvh_probe_pmf"], np.float32).view(np.uint32))
+    hit = light >= 0
+    assert hit.sum() > n // 2
+    # for a light of the tree Sample's probability is PMF(light) up to the order of the products
+    # (infinite lights: PMF is exact)
+    np.testing.assert_allclose(pmf[hit, 0], pmf[hit, 1], rtol=2e-6)
+    nl = len(d["lights_i"])
+    assert len(set(light[hit].tolist())) > min(nl, 20) // 2  # the descent reaches many different lights
