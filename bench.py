@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true", help="skip the config-1 end-to-end render section")
     ap.add_argument("--render-cpu-spp", type=int, default=64, help="spp of the bounded pbrt_ref sample")
+    ap.add_argument("--no-config3", action="store_true", help="skip the config-3 (10M instanced triangles) section")
+    ap.add_argument("--config3-spp", type=int, default=32, help="spp of config 3's frame rendered per step")
+    ap.add_argument("--config3-cpu-spp", type=int, default=2, help="spp of the bounded pbrt_ref sample of config 3")
     return ap.parse_args()
 
 
@@ -205,6 +208,186 @@ def render_section(args, P, torch, dist, rank, world, local, stream, barrier):
     return out
 
 
+CONFIG3_CASE = "config3_full"  # BASELINE.json configs[2]; tables in tests/golden (make_golden.py CONFIG3_FULL)
+
+
+def config3_rays(P, rsc, n, seed):
+    """Primary rays of the scene's own perspective camera (jittered over the whole frame, n of them)."""
+    d = rsc.d
+    rng = np.random.default_rng(seed)
+    w, h = rsc.resolution
+    cfr = np.asarray(d["camera_from_raster"], np.float64).reshape(4, 4)
+    rfc = np.asarray(d["render_from_camera"], np.float64).reshape(4, 4)
+    pf = np.stack([rng.uniform(0, w, n), rng.uniform(0, h, n), np.zeros(n), np.ones(n)], axis=1)
+    pc = pf @ cfr.T
+    pc = pc[:, :3] / pc[:, 3:4]
+    dirs = pc / np.linalg.norm(pc, axis=1, keepdims=True)
+    rays = np.empty((n, 7), np.float32)
+    rays[:, 0:3] = rfc[:3, 3]
+    rays[:, 3:6] = dirs @ rfc[:3, :3].T
+    rays[:, 6] = np.inf
+    return rays
+
+
+def config3_shadow_rays(P, rsc, prim, hits, seed):
+    """From each primary hit towards a random emitter of the scene (unnormalised d, tMax = 1 - 1e-4, as
+    pbrt's SpawnRayTo); rays that escaped start at a random point above the ground instead."""
+    d = rsc.d
+    rng = np.random.default_rng(seed)
+    n = len(prim)
+    li = d["lights_i"]
+    li = li[li[:, 0] >= 0]
+    first = np.concatenate([[0], np.cumsum(d["mesh_nverts"].astype(np.int64))[:-1]])
+    tfirst = np.concatenate([[0], np.cumsum(d["mesh_ntris"].astype(np.int64))[:-1]])
+    tri = d["indices"][tfirst[li[:, 0]] + li[:, 1]] + first[li[:, 0]][:, None]
+    cent = d["P"][tri].mean(axis=1)  # emitters are world-level meshes: render-space vertices
+    target = cent[rng.integers(0, len(cent), n)]
+    miss = hits["mesh"] == 0xFFFFFFFF
+    t = np.where(miss, 0.0, hits["t"]).astype(np.float32)
+    o = prim[:, 0:3] + prim[:, 3:6] * t[:, None]
+    # (render space is camera-world: the world origin sits at -eye = (0, -14, 48))
+    o[miss] = np.stack([rng.uniform(-30, 30, miss.sum()), rng.uniform(0.2, 10, miss.sum()) - 14.0,
+                        rng.uniform(-30, 30, miss.sum()) + 48.0], axis=1)
+    dirn = target - o
+    o = o + dirn * 1e-4  # step off the surface
+    rays = np.empty((n, 7), np.float32)
+    rays[:, 0:3] = o
+    rays[:, 3:6] = target - o
+    rays[:, 6] = 1 - 1e-4
+    return rays
+
+
+def config3_section(args, P, torch, dist, rank, world, local, stream, barrier):
+    """BASELINE configs[2], the north_star's headline scene: ~10 M instanced triangles (32 definitions x 2048
+    triangles x 4883 placements), glass / metal / coated / diffuse, 2048 emitters through the light BVH.
+    (a) traversal of camera + shadow rays, weak scaling like the main line; (b) the frame at
+    --config3-spp of its 1024 spp per step, sample stripes over the ranks."""
+    rsc = P.RenderScene.load(os.path.join(ROOT, "tests", "golden", CONFIG3_CASE + ".b2rs"))
+    geo = rsc.geometry
+    agg = P.B200Aggregate(geo, device=local, stream=stream.cuda_stream)
+    st = agg.stats()
+    n = args.rays
+    prim = config3_rays(P, rsc, n, seed=11 + rank)
+    hits = np.empty(n, dtype=P.capi.HIT_DTYPE)
+    for a in range(0, n, 1 << 22):
+        hits[a:a + (1 << 22)] = agg.IntersectClosest(prim[a:a + (1 << 22)])
+    shad = config3_shadow_rays(P, rsc, prim, hits, seed=1011 + rank)
+    sample = slice(0, min(n, 1 << 22))
+    agg.IntersectClosest(prim[sample], counters=True)
+    tc = agg.trace_stats()
+    agg.IntersectShadow(shad[sample], counters=True)
+    ta = agg.trace_stats()
+    d_prim, d_shad = torch.from_numpy(prim).cuda(), torch.from_numpy(shad).cuda()
+    d_hits = torch.empty(n * 24, dtype=torch.uint8, device="cuda")
+    d_occ = torch.empty(n, dtype=torch.uint8, device="cuda")
+    for _ in range(args.warmup):
+        agg.intersect_closest_ptr(d_prim.data_ptr(), n, d_hits.data_ptr(), P.capi.MEM_DEVICE)
+        agg.intersect_any_ptr(d_shad.data_ptr(), n, d_occ.data_ptr(), P.capi.MEM_DEVICE)
+    barrier()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 1)]
+    ev[0].record(stream)
+    for k in range(args.steps):
+        agg.intersect_closest_ptr(d_prim.data_ptr(), n, d_hits.data_ptr(), P.capi.MEM_DEVICE)
+        ev[2 * k + 1].record(stream)
+        agg.intersect_any_ptr(d_shad.data_ptr(), n, d_occ.data_ptr(), P.capi.MEM_DEVICE)
+        ev[2 * k + 2].record(stream)
+    barrier()
+    ms_closest = float(np.mean([ev[2 * k].elapsed_time(ev[2 * k + 1]) for k in range(args.steps)]))
+    ms_any = float(np.mean([ev[2 * k + 1].elapsed_time(ev[2 * k + 2]) for k in range(args.steps)]))
+    hit_frac = float((np.frombuffer(d_hits.cpu().numpy(), dtype=P.capi.HIT_DTYPE)["mesh"] != 0xFFFFFFFF).mean())
+    occ_frac = float(d_occ.float().mean().item())
+    del d_prim, d_shad, d_hits, d_occ
+    agg.close()
+
+    # ---- the frame
+    spp = min(args.config3_spp, rsc.spp)
+    r = P.B200Renderer(rsc, device=local, stream=stream.cuda_stream)
+    ptr, nd = r.film_device_ptr()
+    film_t = torch.as_tensor(_DevArray(ptr, nd, "<f8"), device="cuda")
+
+    def frame(read):
+        r.clear()
+        r.render(*P.parallel.sample_stripe(spp, rank, world))
+        P.parallel.reduce_film(film_t, dist)
+        return r.image() if (read and rank == 0) else None
+
+    for _ in range(min(args.warmup, 3)):
+        frame(False)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        frame(False)
+    e1.record(stream)
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    rst = r.stats()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        img = frame(True)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    r.close()
+    t = torch.tensor([ms_closest, ms_any, dev_ms, e2e_s], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_closest, ms_any, dev_ms, e2e_s = (float(x) for x in t.cpu())
+    if rank != 0:
+        return None
+    w, h = rsc.resolution
+    ns = w * h * spp * args.steps
+    peak, _ = peaks()
+    NODE_B, PRIM_B = 32, 48
+    bytes_closest = 28 + 24 + (NODE_B * tc["nodes_visited"] + PRIM_B * tc["prims_tested"]) / tc["rays"]
+    ntri = int(sum(len(m.indices) for m in geo.meshes if m.object < 0) +
+               sum(sum(len(m.indices) for m in geo.meshes if m.object == i.object) for i in geo.instances))
+    out = {"workload": f"config3: {ntri} instanced triangles ({len(geo.instances)} placements of "
+                       f"{len(set(i.object for i in geo.instances))} object definitions), {len(rsc.d['lights_i'])} lights, "
+                       f"{w}x{h}; traversal: {n} camera rays + {n} shadow rays towards emitters per step per rank",
+           "triangles": ntri,
+           "traversal": {"metric": METRIC, "unit": UNIT,
+                         "value": 2 * n * world / ((ms_closest + ms_any) * 1e-3) * 1e-6,
+                         "closest_mrays_per_s": n * world / (ms_closest * 1e-3) * 1e-6,
+                         "any_mrays_per_s": n * world / (ms_any * 1e-3) * 1e-6,
+                         "nodes_per_ray": tc["nodes_visited"] / tc["rays"], "prims_per_ray": tc["prims_tested"] / tc["rays"],
+                         "nodes_per_ray_any": ta["nodes_visited"] / ta["rays"],
+                         "bytes_per_ray": bytes_closest,
+                         "roofline_frac": bytes_closest * n / (ms_closest * 1e-3) * 1e-9 / peak,
+                         "hit_fraction": hit_frac, "occluded_fraction": occ_frac,
+                         "device_bytes": st["device_bytes"], "build_s": st["build_seconds"]},
+           "render": {"metric": "render_msamples_per_s", "unit": "Msamples/s", "value": ns / (dev_ms * 1e-3) * 1e-6,
+                      "ms_per_frame": dev_ms / args.steps, "scaling": "strong",
+                      "sample": f"{spp} of the frame's {rsc.spp} spp per step (sample indices 0..{spp - 1}), path maxdepth 5, "
+                                f"bvh light sampler; sample stripes over {world} rank(s), film reduced by NCCL",
+                      "e2e": {"value": ns / e2e_s * 1e-6, "unit": "Msamples/s", "h2d_bytes_per_step": 0,
+                              "d2h_bytes_per_step": w * h * 12},
+                      "rays_per_frame": (rst["closest_rays"] + rst["shadow_rays"]) * world,
+                      "launches_per_frame": rst["kernel_launches"], "image_mean": float(img.mean())}}
+    if not args.no_cpu_baseline:
+        out["render"]["cpu_baseline"] = config3_cpu_reference(args, P)
+    return out
+
+
+def config3_cpu_reference(args, P):
+    """pbrt_ref on a bounded sample of config 3: the whole scene and frame at --config3-cpu-spp samples per pixel."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refrun
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    if not refrun.render_available():
+        return {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    import make_golden
+    kw = dict(make_golden.CONFIG3_FULL, spp=args.config3_cpu_spp)
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt, pfm = os.path.join(tmp, "c3.pbrt"), os.path.join(tmp, "c3.pfm")
+        P.scenes.config3_pbrt(pbrt, out=pfm, **kw)
+        _, secs = refrun.render(pbrt, pfm)
+    n = kw["res"][0] * kw["res"][1] * kw["spp"]
+    return {"value": n / secs * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
+            "seconds": secs,
+            "sample": f"the config-3 scene at {kw['res'][0]}x{kw['res'][1]}, {kw['spp']} spp (config 3 is 1024 spp), wall "
+                      f"clock of the whole pbrt_ref process incl. parse + BVH builds"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU BVHAggregate on all host cores, bounded sample per step."""
     if rank != 0:
@@ -344,6 +527,13 @@ def main():
     if not args.no_render:
         render = render_section(args, P, torch, dist, rank, world, local, stream, barrier)
 
+    config3 = None
+    if not args.no_config3:
+        agg.close()
+        agg = None
+        del d_prim, d_shad, d_hits, d_occ
+        config3 = config3_section(args, P, torch, dist, rank, world, local, stream, barrier)
+
     # ---- max over ranks
     t = torch.tensor([total_ms, e2e_s, ms_closest, ms_any], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -372,6 +562,7 @@ def main():
                     "h2d_bytes_per_step": 2 * n * 28, "d2h_bytes_per_step": n * 24 + n},
             "gpu_launches": 2 * args.steps,
             "render": render,
+            "config3": config3,
             "clocks": clk,
             "scene": {"bvh2_nodes": st["n_bvh2_nodes"], "wide_nodes": st["n_wide_nodes"],
                       "device_bytes": st["device_bytes"], "build_s": st["build_seconds"]},
@@ -379,7 +570,8 @@ def main():
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, P, sc, prim, shad)
         print(json.dumps(line), flush=True)
-    agg.close()
+    if agg is not None:
+        agg.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -105,10 +105,18 @@ static std::vector<float> Mat(const SquareMatrix<4> &m) {
 struct SpectraPool {
     std::vector<float> values;
     std::vector<uint32_t> interp;
+    std::map<std::vector<uint32_t>, int> seen;  // tables equal bit for bit are stored once
     int add(Spectrum s, uint32_t mode) {
-        for (int l = 395; l <= 705; ++l) values.push_back(s(Float(l)));
+        std::vector<uint32_t> key(312);
+        float t[311];
+        for (int l = 395; l <= 705; ++l) t[l - 395] = s(Float(l));
+        memcpy(key.data(), t, sizeof(t));
+        key[311] = mode;
+        auto it = seen.find(key);
+        if (it != seen.end()) return it->second;
+        values.insert(values.end(), t, t + 311);
         interp.push_back(mode);
-        return int(interp.size()) - 1;
+        return seen[key] = int(interp.size()) - 1;
     }
 };
 
@@ -223,6 +231,8 @@ int main(int argc, char **argv) {
     }
 
     Writer w(argv[2]);
+    // `--no-bvh`: leave the reference's BVHs out (large scenes; our host builds the same trees itself)
+    const bool dumpBvh = !(argc > 3 && std::string(argv[3]) == "--no-bvh");
     SpectraPool pool;
 
     // ---- camera (perspective only for now)
@@ -407,7 +417,7 @@ int main(int argc, char **argv) {
         w.i32("instance_object", {uint32_t(instObject.size())}, instObject);
         w.f32("instance_m", {uint32_t(instObject.size()), 16}, instM);
         w.f32("instance_minv", {uint32_t(instObject.size()), 16}, instMInv);
-        for (size_t k = 0; k < objNodes.size(); ++k) {
+        for (size_t k = 0; dumpBvh && k < objNodes.size(); ++k) {
             w.u32("obj_bvh_nodes_" + std::to_string(k), {uint32_t(objNodes[k].size() / 8), 8}, objNodes[k]);
             w.u32("obj_bvh_prims_" + std::to_string(k), {uint32_t(objPrims[k].size() / 3), 3}, objPrims[k]);
         }
@@ -415,8 +425,10 @@ int main(int argc, char **argv) {
     int nNodes = countNodes(bvh->nodes);
     std::vector<uint32_t> nodeWords(size_t(nNodes) * 8);
     memcpy(nodeWords.data(), bvh->nodes, size_t(nNodes) * 32);
-    w.u32("bvh_nodes", {uint32_t(nNodes), 8}, nodeWords);
-    w.u32("bvh_prims", {uint32_t(bvhPrims.size() / 3), 3}, bvhPrims);
+    if (dumpBvh) {
+        w.u32("bvh_nodes", {uint32_t(nNodes), 8}, nodeWords);
+        w.u32("bvh_prims", {uint32_t(bvhPrims.size() / 3), 3}, bvhPrims);
+    }
 
     // ---- materials
     std::vector<int32_t> matI;

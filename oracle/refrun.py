@@ -101,9 +101,10 @@ def render(pbrt_file, out_pfm, nthreads=None, timeout=3600):
     return read_pfm(out_pfm), dt
 
 
-def dump_scene(pbrt_file, out_b2rs):
-    """Scene tables as the reference's own parser + object creation produced them (dumpscene_ref.cpp)."""
-    r = subprocess.run([DUMPSCENE, pbrt_file, out_b2rs], capture_output=True, text=True,
+def dump_scene(pbrt_file, out_b2rs, bvh=True):
+    """Scene tables as the reference's own parser + object creation produced them (dumpscene_ref.cpp).
+    bvh=False leaves the reference's BVH node arrays out of the file."""
+    r = subprocess.run([DUMPSCENE, pbrt_file, out_b2rs] + ([] if bvh else ["--no-bvh"]), capture_output=True, text=True,
                        cwd=os.path.dirname(pbrt_file))
     if r.returncode != 0:
         raise RuntimeError(f"dumpscene_ref failed ({r.returncode}): {r.stderr[-2000:]}")

@@ -373,6 +373,89 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
     return sc
 
 
+def _bumpy_torus(rng, nu=32, nv=32):
+    """Closed surface without poles, 2 * nu * nv triangles inside [-1/2, 1/2]^3: a torus whose tube radius
+    is modulated by a few random harmonics."""
+    u = np.arange(nu) * (2 * np.pi / nu)
+    v = np.arange(nv) * (2 * np.pi / nv)
+    U, V = np.meshgrid(u, v, indexing="ij")
+    r = np.full_like(U, 0.13)
+    for _ in range(4):
+        a, b = rng.integers(1, 5, 2)
+        r += rng.uniform(-0.025, 0.025) * np.cos(a * U + b * V + rng.uniform(0, 2 * np.pi))
+    R = 0.3
+    x = (R + r * np.cos(V)) * np.cos(U)
+    z = (R + r * np.cos(V)) * np.sin(U)
+    y = r * np.sin(V) * rng.uniform(0.6, 1.4)
+    p = np.stack([x, y, z], axis=-1).reshape(-1, 3).astype(np.float32)
+    i, j = np.meshgrid(np.arange(nu), np.arange(nv), indexing="ij")
+    a = (i * nv + j).reshape(-1)
+    b = (((i + 1) % nu) * nv + j).reshape(-1)
+    c = (((i + 1) % nu) * nv + (j + 1) % nv).reshape(-1)
+    d = (i * nv + (j + 1) % nv).reshape(-1)
+    idx = np.concatenate([np.stack([a, b, c], 1), np.stack([a, c, d], 1)]).astype(np.int32)
+    return Mesh(p, idx)
+
+
+CONFIG3_MATERIALS = ["dielectric_smooth", "conductor_rough", "coated_diffuse", None, "dielectric_rough",
+                     "conductor_smooth", "coated_diffuse_rough", "conductor_reflectance"]
+
+
+def config3_pbrt(path, n_objects=32, grid=32, n_instances=4883, n_lights=1024, res=(1920, 1080), spp=1024,
+                 maxdepth=5, out="config3.pfm", seed=0, crop=None):
+    """BASELINE configs[2]: procedural instanced scene (n_instances x 2 * grid^2 triangles ~ 10 M at the
+    defaults) of dielectric / conductor / coated / diffuse objects over a ground plane, lit by n_lights
+    small emissive quads (2 triangles each) through the light-BVH sampler, plus a dim uniform sky.
+    Every object definition carries one material; instances are rotation x uniform scale x translation.
+    crop = (x0, x1, y0, y1) in NDC renders a window of the frame (for the bounded CPU baseline)."""
+    rng = np.random.default_rng(3000 + n_objects * 7 + n_instances)
+    lines = [
+        'LookAt 0 14 -48  0 3 0  0 1 0',
+        'Camera "perspective" "float fov" 38',
+        f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
+        f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "bvh"',
+        'PixelFilter "box"',
+        f'Film "rgb" "string filename" "{out}" "integer xresolution" {res[0]} "integer yresolution" {res[1]} '
+        '"bool savefp16" false' + (f' "float cropwindow" [{crop[0]} {crop[1]} {crop[2]} {crop[3]}]' if crop else ''),
+        'WorldBegin',
+        'LightSource "infinite" "rgb L" [0.03 0.04 0.06]',
+        'AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.45 0.42 0.38]',
+        '  ' + _mesh_pbrt(_quad([-60, 0, -60], [-60, 0, 60], [60, 0, 60], [60, 0, -60])), 'AttributeEnd',
+    ]
+    for o in range(n_objects):
+        mat = CONFIG3_MATERIALS[o % len(CONFIG3_MATERIALS)]
+        c = rng.uniform(0.2, 0.8, 3)
+        lines += ['AttributeBegin',
+                  '  ' + (MATERIALS[mat] if mat else f'Material "diffuse" "rgb reflectance" [{c[0]:.3f} {c[1]:.3f} {c[2]:.3f}]'),
+                  f'  ObjectBegin "obj{o}"', '    ' + _mesh_pbrt(_bumpy_torus(rng, grid, grid)), '  ObjectEnd', 'AttributeEnd']
+    for i in range(n_instances):
+        t = (rng.uniform(-30, 30), rng.uniform(0.6, 9.0), rng.uniform(-30, 30))
+        axis = rng.normal(size=3)
+        axis /= np.linalg.norm(axis)
+        lines += ['AttributeBegin', f'  Translate {t[0]:.5f} {t[1]:.5f} {t[2]:.5f}',
+                  f'  Rotate {rng.uniform(0, 360):.4f} {axis[0]:.5f} {axis[1]:.5f} {axis[2]:.5f}',
+                  f'  Scale {rng.uniform(0.8, 2.2):.5f} ' * 1, ]
+        sc = lines.pop().split()[1]
+        lines += [f'  Scale {sc} {sc} {sc}', f'  ObjectInstance "obj{i % n_objects}"', 'AttributeEnd']
+    palette = [rng.uniform(20.0, 200.0) * rng.uniform(0.3, 1.0, 3) for _ in range(32)]  # 32 emission spectra
+    for k in range(n_lights):
+        c = np.array([rng.uniform(-32, 32), rng.uniform(5.0, 14.0), rng.uniform(-32, 32)])
+        n = rng.normal(size=3) * 0.5 + np.array([0.0, -1.0, 0.0])
+        n /= np.linalg.norm(n)
+        a = np.cross(n, [1.0, 0.0, 0.0])
+        a /= np.linalg.norm(a)
+        b = np.cross(n, a)
+        h = rng.uniform(0.1, 0.3)
+        q = [c - h * a - h * b, c + h * a - h * b, c + h * a + h * b, c - h * a + h * b]
+        L = palette[k % 32]
+        pts = " ".join(f"{float(v):.7g}" for pt in q for v in pt)
+        lines += ['AttributeBegin', f'  AreaLightSource "diffuse" "rgb L" [{L[0]:.5g} {L[1]:.5g} {L[2]:.5g}]',
+                  '  Material "diffuse" "rgb reflectance" [0 0 0]',
+                  f'  Shape "trianglemesh" "point3 P" [{pts}] "integer indices" [0 1 2 0 2 3]', 'AttributeEnd']
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+
+
 def load_b2rs(path):
     """Reads the named-array container written by a host adaptor (oracle/dumpscene_ref.cpp is the
     test-side one): 'B2RS', u32 count, {u32 nameLen, name, u32 dtype, u32 ndim, u32 dims[], data}."""

@@ -79,6 +79,10 @@ NOISE_GATED = {"cornell_glass_r64_s16", "cornell_metal2_r48_s8", "cornell_coated
 TABLE_CASES = {
     "cornell_r512_s64": dict(res=512, spp=64, maxdepth=5, lightsampler="power", seed=0),
 }
+# BASELINE.json configs[2] (scenes.config3_pbrt): full size as tables only (bench.py), and in miniature with
+# reference images (noise-gated: the scene has smooth glass, see NOISE_GATED)
+CONFIG3_FULL = dict(n_objects=32, grid=32, n_instances=4883, n_lights=1024, res=(1920, 1080), spp=1024, maxdepth=5)
+CONFIG3_SMALL = dict(n_objects=8, grid=12, n_instances=300, n_lights=96, res=(96, 54), spp=16, maxdepth=5)
 
 
 def make_render_goldens(P, refrun, out):
@@ -95,6 +99,18 @@ def make_render_goldens(P, refrun, out):
                 img2, _ = refrun.render(pbrt, pfm)
                 np.save(os.path.join(out, name + "_ref2.npy"), img2.astype(np.float32))
             print(name, img.shape, "mean", img.mean(axis=(0, 1)), f"{secs:.2f}s")
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt, pfm = os.path.join(tmp, "c3.pbrt"), os.path.join(tmp, "c3.pfm")
+        P.scenes.config3_pbrt(pbrt, out=pfm, **CONFIG3_FULL)
+        refrun.dump_scene(pbrt, os.path.join(out, "config3_full.b2rs"), bvh=False)
+        print("config3_full tables only")
+        for seed, suffix in ((0, "_ref.npy"), (1, "_ref2.npy")):
+            P.scenes.config3_pbrt(pbrt, out=pfm, seed=seed, **CONFIG3_SMALL)
+            if seed == 0:
+                refrun.dump_scene(pbrt, os.path.join(out, "config3_small.b2rs"))
+            img, secs = refrun.render(pbrt, pfm)
+            np.save(os.path.join(out, "config3_small" + suffix), img.astype(np.float32))
+        print("config3_small", img.shape, "mean", img.mean(axis=(0, 1)))
     for name, kw in TABLE_CASES.items():
         with tempfile.TemporaryDirectory() as tmp:
             pbrt = os.path.join(tmp, name + ".pbrt")

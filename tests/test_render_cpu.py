@@ -46,10 +46,12 @@ def noise_gate(img, ref, ref2):
     return rrmse(img, ref) <= 1.25 * floor and abs(img.mean() - ref.mean()) <= 0.01 * ref.mean(), floor
 
 
-def test_golden_image_coated(P, rendercheck):
-    """CoatedDiffuse (LayeredBxDF random walks; smooth and rough coats).  Noise gate, and the measured
-    distance stays a small fraction of the floor because nearly all walks are the reference's."""
-    name = "cornell_coated_r64_s16"
+@pytest.mark.parametrize("name", ["cornell_coated_r64_s16", "config3_small"])
+def test_golden_image_noise_gated(P, rendercheck, name):
+    """CoatedDiffuse (LayeredBxDF random walks; smooth and rough coats), and BASELINE configs[2] in miniature
+    (instanced glass / metal / coated objects, 192 emitters through the light BVH, a uniform sky).  Noise
+    gate, and the measured distance stays a small fraction of the floor because nearly all paths are the
+    reference's."""
     rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
     ref, ref2 = (np.load(os.path.join(GOLD, name + s)) for s in ("_ref.npy", "_ref2.npy"))
     img = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
