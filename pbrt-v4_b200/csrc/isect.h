@@ -24,6 +24,13 @@
 #else
 #define B2_HD_NOINLINE __host__ __device__ __forceinline__
 #endif
+// really out of line: the layered BxDF's walks call the interface routines from a dozen sites; inlined,
+// the coated shade kernel is 48 K instructions and starves on instruction fetch (profiles/)
+#ifdef B2_INLINE_ALL
+#define B2_HD_CALL __host__ __device__ __forceinline__
+#else
+#define B2_HD_CALL __host__ __device__ __noinline__
+#endif
 #define B2_MUL(a, b) __fmul_rn((a), (b))
 #define B2_ADD(a, b) __fadd_rn((a), (b))
 #define B2_SUB(a, b) __fsub_rn((a), (b))
@@ -36,9 +43,11 @@
 #if defined(__CUDACC__)
 #define B2_HD __host__ __device__ inline
 #define B2_HD_NOINLINE __host__ __device__ inline
+#define B2_HD_CALL __host__ __device__ inline
 #else
 #define B2_HD inline
 #define B2_HD_NOINLINE inline
+#define B2_HD_CALL inline
 #endif
 #define B2_MUL(a, b) ((a) * (b))
 #define B2_ADD(a, b) ((a) + (b))

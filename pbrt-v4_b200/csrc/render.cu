@@ -183,9 +183,12 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
         if (type == m) pb.matQ[m][QueuePush(counts + 2 + m)] = t;
 }
 
+#ifndef B2_SHADE_MIN_BLOCKS
+#define B2_SHADE_MIN_BLOCKS 4  // 128 registers: the layered walks are latency bound, four blocks per SM beat three
+#endif
 // ---- one path vertex: PathIntegrator::Li loop body (cpu/integrators.cpp:640-760)
-template <int MAT>
-__global__ void __launch_bounds__(kShadeBlock)
+template <int MAT, int LBVH>
+__global__ void __launch_bounds__(kShadeBlock, B2_SHADE_MIN_BLOCKS)
 ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     int *counts = pb.counts + kCountStride * depth;
@@ -213,7 +216,7 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     uint2 h0 = h[0], h1 = h[1], h2 = h[2];
     hit[0] = h0.x; hit[1] = h0.y; hit[2] = h1.x; hit[3] = h1.y; hit[4] = h2.x; hit[5] = h2.y;
     DevIO io(pb, path, counts + 1, myBeta);
-    ShadeVertex<DevIO, MAT>(rs, p, hit, io);
+    ShadeVertex<DevIO, MAT, LBVH>(rs, p, hit, io);
     if (p.flags & PF_ALIVE) {
         int *next = pb.counts + kCountStride * (depth + 1);
         int slot = QueuePush(next);
@@ -312,22 +315,20 @@ cudaError_t LaunchClassify(const RenderSceneDev &rs, const PassBuffers &pb, int 
 cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width,
                         int nActive, uint32_t matMask, cudaStream_t stream, int *launches) {
     int grid = Blocks(nActive, kShadeBlock);
-    if (matMask & 1u) {
-        ShadeKernel<MAT_DIFFUSE><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
-        ++*launches;
+    const bool lbvh = rs.integrator.lightSampler == 2;
+#define B2_SHADE(bit, MAT)                                                                              \
+    if (matMask & (bit)) {                                                                              \
+        if (lbvh)                                                                                       \
+            ShadeKernel<MAT, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);       \
+        else                                                                                            \
+            ShadeKernel<MAT, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);       \
+        ++*launches;                                                                                    \
     }
-    if (matMask & 2u) {
-        ShadeKernel<MAT_CONDUCTOR><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
-        ++*launches;
-    }
-    if (matMask & 4u) {
-        ShadeKernel<MAT_DIELECTRIC><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
-        ++*launches;
-    }
-    if (matMask & 8u) {
-        ShadeKernel<MAT_COATED_DIFFUSE><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
-        ++*launches;
-    }
+    B2_SHADE(1u, MAT_DIFFUSE)
+    B2_SHADE(2u, MAT_CONDUCTOR)
+    B2_SHADE(4u, MAT_DIELECTRIC)
+    B2_SHADE(8u, MAT_COATED_DIFFUSE)
+#undef B2_SHADE
     return cudaGetLastError();
 }
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {

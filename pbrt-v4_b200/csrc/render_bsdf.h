@@ -189,7 +189,7 @@ struct Bsdf {
 // materials call their top interface with Importance mode and with one of the two lobes masked out.
 enum : uint32_t { SF_REFLECTION = 1, SF_TRANSMISSION = 2, SF_ALL = 3 };
 
-B2_HD float DielF(float eta, const TRDist &tr, V3 wo, V3 wi, bool radiance) {
+B2_HD_CALL float DielF(float eta, TRDist tr, V3 wo, V3 wi, bool radiance) {
     if (eta == 1 || TRSmooth(tr)) return 0;
     float cosTheta_o = CosTheta(wo), cosTheta_i = CosTheta(wi);
     bool reflect = cosTheta_i * cosTheta_o > 0;
@@ -207,7 +207,7 @@ B2_HD float DielF(float eta, const TRDist &tr, V3 wo, V3 wi, bool radiance) {
     return ft;
 }
 
-B2_HD float DielPDF(float eta, const TRDist &tr, V3 wo, V3 wi, uint32_t sflags) {
+B2_HD_CALL float DielPDF(float eta, TRDist tr, V3 wo, V3 wi, uint32_t sflags) {
     if (eta == 1 || TRSmooth(tr)) return 0;
     float cosTheta_o = CosTheta(wo), cosTheta_i = CosTheta(wi);
     bool reflect = cosTheta_i * cosTheta_o > 0;
@@ -227,7 +227,7 @@ B2_HD float DielPDF(float eta, const TRDist &tr, V3 wo, V3 wi, uint32_t sflags) 
 }
 
 // returns the sample; `f` is the (wavelength-independent) BSDF value
-B2_HD BsdfSample DielSample(float eta, const TRDist &tr, V3 wo, float uc, float u0, float u1, bool radiance,
+B2_HD_CALL BsdfSample DielSample(float eta, TRDist tr, V3 wo, float uc, float u0, float u1, bool radiance,
                             uint32_t sflags, float &f) {
     BsdfSample s{false, mk(0, 0, 0), 0, 0, 1, false};
     f = 0;

@@ -160,6 +160,10 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("light BVH node refers outside its tables");
         }
         out.lightBvhNodes.assign(nodes, nodes + 8 * size_t(d->n_light_bvh_nodes));
+        // allLightBounds rides behind the last node, so the sampler hands plain pointers to its helpers
+        uint32_t tail[8] = {};
+        std::memcpy(tail, d->light_bvh_bounds, 24);
+        out.lightBvhNodes.insert(out.lightBvhNodes.end(), tail, tail + 8);
         out.lightBitTrails.assign(d->light_bit_trails, d->light_bit_trails + d->n_lights);
         rs.nLightBvhNodes = d->n_light_bvh_nodes;
         std::memcpy(rs.lightBvhBounds, d->light_bvh_bounds, 24);

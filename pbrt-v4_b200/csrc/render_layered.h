@@ -124,7 +124,7 @@ B2_HD float DiffFScalar(V3 wo, V3 wi) { return SameHemisphere(wo, wi) ? kInvPi :
 B2_HD float DiffPDF(V3 wo, V3 wi) { return SameHemisphere(wo, wi) ? AbsCosTheta(wi) * kInvPi : 0.f; }
 
 // LayeredBxDF::f (bxdfs.h:608-790), Radiance mode.  Result: ev.poly (already divided by nSamples).
-B2_HD BsdfEval CoatedF(const Bsdf &b, V3 wo, V3 wi, int32_t seed) {
+B2_HD_CALL BsdfEval CoatedF(const Bsdf &b, V3 wo, V3 wi, int32_t seed) {
     BsdfEval ev = ZeroEval();
     for (int i = 0; i < kLayerPoly; ++i) ev.poly[i] = 0;
     if (wo.z < 0) {  // twoSided
@@ -201,7 +201,7 @@ B2_HD BsdfEval CoatedF(const Bsdf &b, V3 wo, V3 wi, int32_t seed) {
 }
 
 // LayeredBxDF::Sample_f (bxdfs.h:792-905), Radiance mode, all lobes.
-B2_HD BsdfSample CoatedSample(const Bsdf &b, V3 wo, float uc, float u0, float u1, int32_t seed, BsdfEval &ev) {
+B2_HD_CALL BsdfSample CoatedSample(const Bsdf &b, V3 wo, float uc, float u0, float u1, int32_t seed, BsdfEval &ev) {
     BsdfSample out{false, mk(0, 0, 0), 0, 0, 1, false};
     ev = ZeroEval();
     for (int i = 0; i < kLayerPoly; ++i) ev.poly[i] = 0;
@@ -280,7 +280,7 @@ B2_HD BsdfSample CoatedSample(const Bsdf &b, V3 wo, float uc, float u0, float u1
 }
 
 // LayeredBxDF::PDF (bxdfs.h:907-1011), all lobes.
-B2_HD float CoatedPDF(const Bsdf &b, V3 wo, V3 wi, int32_t seed) {
+B2_HD_CALL float CoatedPDF(const Bsdf &b, V3 wo, V3 wi, int32_t seed) {
     if (wo.z < 0) {
         wo = -wo;
         wi = -wi;

@@ -32,7 +32,10 @@ B2_HD V3 OctahedralDecode(uint32_t packed) {  // util/vecmath.h:1752-1766
 }
 
 // CompactLightBounds::Importance(p, n, allb)
-B2_HD_NOINLINE float LightBoundsImportance(const LightBvhNode &nd, const float *allb, V3 p, V3 n) {
+// nd: one node; allb: allLightBounds, six floats (both in the node table: plain pointers keep the
+// caller's scene block out of local memory)
+B2_HD_CALL float LightBoundsImportance(const LightBvhNode *ndp, const float *allb, V3 p, V3 n) {
+    const LightBvhNode nd = *ndp;
     // Bounds(allb): lightsamplers.h:133-142
     float lo[3], hi[3];
     uint32_t q[6] = {nd.w[3] & 0xFFFFu, nd.w[3] >> 16, nd.w[4] & 0xFFFFu, nd.w[4] >> 16, nd.w[5] & 0xFFFFu,
@@ -95,6 +98,7 @@ B2_HD int LightBvhSample(const RenderSceneDev &rs, V3 p, V3 n, float u, float *p
     const LightBvhNode *nodes = reinterpret_cast<const LightBvhNode *>(rs.lightBvhNodes);
     int nInf = (int)rs.nInfiniteLights;
     bool haveNodes = rs.nLightBvhNodes > 0;
+    const float *allb = reinterpret_cast<const float *>(nodes + rs.nLightBvhNodes);
     float pInfinite = float(nInf) / float(nInf + (haveNodes ? 1 : 0));
     if (u < pInfinite) {
         u /= pInfinite;
@@ -108,12 +112,11 @@ B2_HD int LightBvhSample(const RenderSceneDev &rs, V3 p, V3 n, float u, float *p
     int nodeIndex = 0;
     float prob = 1 - pInfinite;
     while (true) {
-        LightBvhNode node = nodes[nodeIndex];
-        uint32_t link = node.w[6];
+        uint32_t link = nodes[nodeIndex].w[6];
         if (!(link >> 31)) {
             int second = (int)(link & 0x7FFFFFFFu);
-            float ci[2] = {LightBoundsImportance(nodes[nodeIndex + 1], rs.lightBvhBounds, p, n),
-                           LightBoundsImportance(nodes[second], rs.lightBvhBounds, p, n)};
+            float ci[2] = {LightBoundsImportance(nodes + nodeIndex + 1, allb, p, n),
+                           LightBoundsImportance(nodes + second, allb, p, n)};
             if (ci[0] == 0 && ci[1] == 0) return -1;
             // SampleDiscrete over two weights (util/sampling.h:79-113)
             float sumWeights = 0;
@@ -121,14 +124,20 @@ B2_HD int LightBvhSample(const RenderSceneDev &rs, V3 p, V3 n, float u, float *p
             sumWeights += ci[1];
             float up = u * sumWeights;
             if (up == sumWeights) up = NextDown(up);
+            // `while (sum + weights[offset] <= up) sum += weights[offset++]` over two weights, without
+            // indexing (the second weight cannot be passed: up < sumWeights)
             int offset = 0;
-            float sum = 0;
-            while (sum + ci[offset] <= up) sum += ci[offset++];
-            prob *= ci[offset] / sumWeights;
-            u = fminf((up - sum) / ci[offset], kOneMinusEps);
+            float sum = 0, wsel = ci[0];
+            if (sum + ci[0] <= up) {
+                sum += ci[0];
+                offset = 1;
+                wsel = ci[1];
+            }
+            prob *= wsel / sumWeights;
+            u = fminf((up - sum) / wsel, kOneMinusEps);
             nodeIndex = (offset == 0) ? nodeIndex + 1 : second;
         } else {
-            if (nodeIndex > 0 || LightBoundsImportance(node, rs.lightBvhBounds, p, n) > 0) {
+            if (nodeIndex > 0 || LightBoundsImportance(nodes + nodeIndex, allb, p, n) > 0) {
                 *pmf = prob;
                 return (int)(link & 0x7FFFFFFFu);
             }
@@ -144,6 +153,7 @@ B2_HD float LightBvhPMF(const RenderSceneDev &rs, V3 p, V3 n, int light) {
     bool haveNodes = rs.nLightBvhNodes > 0;
     uint32_t bitTrail = rs.lightBitTrails[light];
     if (bitTrail == 0xFFFFFFFFu) return 1.f / (nInf + (haveNodes ? 1 : 0));  // not in the map
+    const float *allb = reinterpret_cast<const float *>(nodes + rs.nLightBvhNodes);
     float pInfinite = float(nInf) / float(nInf + (haveNodes ? 1 : 0));
     float pmf = 1 - pInfinite;
     int nodeIndex = 0;
@@ -151,9 +161,9 @@ B2_HD float LightBvhPMF(const RenderSceneDev &rs, V3 p, V3 n, int light) {
         uint32_t link = nodes[nodeIndex].w[6];
         if (link >> 31) return pmf;
         int second = (int)(link & 0x7FFFFFFFu);
-        float ci[2] = {LightBoundsImportance(nodes[nodeIndex + 1], rs.lightBvhBounds, p, n),
-                       LightBoundsImportance(nodes[second], rs.lightBvhBounds, p, n)};
-        pmf *= ci[bitTrail & 1] / (ci[0] + ci[1]);
+        float ci[2] = {LightBoundsImportance(nodes + nodeIndex + 1, allb, p, n),
+                       LightBoundsImportance(nodes + second, allb, p, n)};
+        pmf *= ((bitTrail & 1) ? ci[1] : ci[0]) / (ci[0] + ci[1]);
         nodeIndex = (bitTrail & 1) ? second : nodeIndex + 1;
         bitTrail >>= 1;
     }

@@ -207,8 +207,11 @@ B2_SPECTRAL_LOOP
 // p.ray.  IO: AddL(k, v) adds to the path's radiance; ShadowBegin() / SetLd(k, v) / ShadowEnd(valid,
 // o, d, tMax) record a light sample whose visibility is still unknown; Beta(k) / SetBeta(k, v) are the
 // path throughput.
-template <class IO, int MAT = -1>
+// MAT / LBVH: material type and "the light sampler is the BVH one" fixed at compile time (the kernels);
+// -1 = read from the scene (the host check).
+template <class IO, int MAT = -1, int LBVH = -1>
 B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit[6], IO &io) {
+    const bool lightBvh = LBVH < 0 ? rs.integrator.lightSampler == 2 : LBVH == 1;
     if (hit[0] == kMissTag) {  // escaped ray (cpu/integrators.cpp:645-662); the kernels do this in ClassifyKernel
         if (rs.nInfiniteLights) EscapedRadiance(rs, p.lambdaU, p.depth == 0 || (p.flags & PF_SPECULAR), p.pB, io);
         KillPath(p);
@@ -245,7 +248,7 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
             if (!(p.depth == 0 || (p.flags & PF_SPECULAR))) {
                 float pmf = al.aliasP;  // PowerLightSampler::PMF (lightsamplers.h:78-82)
                 if (rs.integrator.lightSampler == 0) pmf = 1.f / rs.nLights;
-                if (rs.integrator.lightSampler == 2)
+                if (lightBvh)
                     pmf = LightBvhPMF(rs, Mid(p.prev.pi), p.prev.ns, mesh.lightFirst + (int)tv.tri);
                 float p_l = pmf * TrianglePDF(tv, p.prev, p.rayD, al.flipNormal != 0);
                 w = PowerHeuristic(p.pB, p_l);
@@ -308,10 +311,12 @@ B2_SPECTRAL_LOOP
             // AliasTable::Sample (util/sampling.cpp:619-647) / UniformLightSampler (lightsamplers.h:33-53)
             int nl = (int)rs.nLights, lidx;
             float pmf;
-            if (rs.integrator.lightSampler == 0) {
+            if (lightBvh) {
+                lidx = LightBvhSample(rs, Mid(ctx.pi), ctx.ns, uL, &pmf);
+            } else if (rs.integrator.lightSampler == 0) {
                 lidx = (int)fminf(uL * nl, (float)(nl - 1));
                 pmf = 1.f / nl;
-            } else if (rs.integrator.lightSampler == 2) {
+            } else if (false) {
                 lidx = LightBvhSample(rs, Mid(ctx.pi), ctx.ns, uL, &pmf);
             } else {
                 int offset = (int)fminf(uL * nl, (float)(nl - 1));
