@@ -212,7 +212,7 @@ typedef struct b200pt_render_desc {
     float camera_from_raster[16];
     float render_from_camera[16];
     float lens_radius, focal_distance;
-    /* film: RGBFilm (film.h:232-310) with a box filter */
+    /* film: 0 = RGBFilm (film.h:232-310), 1 = SpectralFilm (film.h:430-560; n_buckets below), box filter */
     uint32_t film_type;
     int32_t pixel_bounds[4]; /* x0 y0 x1 y1 */
     int32_t full_resolution[2];
@@ -243,6 +243,11 @@ typedef struct b200pt_render_desc {
     float light_bvh_bounds[6];
     const void *light_bvh_nodes;
     const uint32_t *light_bit_trails;
+    /* SpectralFilm (film_type 1): n_buckets equal bands over [lambda_min, lambda_max]; the wavelengths of a
+     * sample are drawn uniformly over the same range (film.h:443-445), which has to be the build's 395..705 nm
+     * (the ISET 31-band setting); 1 <= n_buckets <= 64. */
+    uint32_t n_buckets;
+    float lambda_min, lambda_max;
 } b200pt_render_desc;
 
 typedef struct b200pt_render b200pt_render;
@@ -262,9 +267,15 @@ int b200pt_render_destroy(b200pt_render *r);
 int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples, int32_t sample_stride);
 int b200pt_film_clear(b200pt_render *r);
 /* film accumulators {rgbSum[3], weightSum} as 4 doubles per pixel, row major over pixel_bounds
- * (RGBFilm::Pixel, film.h:305-310).  device_ptr: for an in-place NCCL reduction by the host. */
+ * (RGBFilm::Pixel, film.h:305-310).  A spectral film appends, after those 4 * n_pixels doubles, n_buckets
+ * planes of bucketSums and n_buckets planes of weightSums, n_pixels doubles each (SpectralFilm::Pixel,
+ * film.h:547-556): n_doubles = n_pixels * (4 + 2 * n_buckets).  device_ptr: for an in-place NCCL reduction
+ * by the host; film_read copies all n_doubles. */
 int b200pt_film_device_ptr(b200pt_render *r, void **ptr, uint64_t *n_doubles);
 int b200pt_film_read(b200pt_render *r, double *rgb_weight);
+/* spectral film only: the S0.* channels of SpectralFilm::GetImage (film.cpp:1221-1273), n_buckets floats per
+ * pixel (bucketSums / weightSums, 0 where no weight). */
+int b200pt_film_spectral_image(b200pt_render *r, float *buckets);
 /* final image, 3 floats per pixel: outputRGBFromSensorRGB * (rgbSum / weightSum) (film.h:261-277) */
 int b200pt_film_image(b200pt_render *r, float *rgb);
 int b200pt_render_get_stats(const b200pt_render *r, b200pt_render_stats *out);

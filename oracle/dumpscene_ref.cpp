@@ -164,6 +164,44 @@ int main(int argc, char **argv) {
         for (auto &light : lights) light.Preprocess(sceneBounds);
     }
 
+    // ---- `dumpscene_ref scene.pbrt --render out.b2rs`: the reference's own render loop body
+    // (ImageTileIntegrator::Render, cpu/integrators.cpp:60-140: EvaluatePixelSample per pixel sample, samples of
+    // a pixel in index order) followed by Film::GetImage, every channel written as float32.  For films whose
+    // file format the oracle build cannot write (spectral film -> EXR).
+    if (std::string(argv[2]) == "--render") {
+        if (argc < 4) die("usage: dumpscene_ref scene.pbrt --render out.b2rs");
+        std::unique_ptr<Integrator> integ(scene.CreateIntegrator(camera, sampler, accel, lights));
+        ImageTileIntegrator *ti = dynamic_cast<ImageTileIntegrator *>(integ.get());
+        if (!ti) die("--render needs an image-tile integrator");
+        Bounds2i pb = film.PixelBounds();
+        int spp = sampler.SamplesPerPixel();
+        ParallelFor2D(pb, [&](Bounds2i tile) {
+            ScratchBuffer scratch(65536);
+            Sampler s = sampler.Clone(Allocator());
+            for (Point2i p : tile)
+                for (int si = 0; si < spp; ++si) {
+                    s.StartPixelSample(p, si);
+                    ti->EvaluatePixelSample(p, si, s, scratch);
+                    scratch.Reset();
+                }
+        });
+        ImageMetadata md;
+        Image im = film.GetImage(&md);
+        int W = im.Resolution().x, H = im.Resolution().y, C = im.NChannels();
+        std::vector<float> px(size_t(W) * H * C);
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x)
+                for (int c = 0; c < C; ++c) px[(size_t(y) * W + x) * C + c] = im.GetChannel(Point2i(x, y), c);
+        Writer w(argv[3]);
+        w.f32("image", {uint32_t(H), uint32_t(W), uint32_t(C)}, px);
+        w.close();
+        std::string names;
+        for (const std::string &n : im.ChannelNames()) names += (names.empty() ? "\"" : ", \"") + n + "\"";
+        printf("{\"width\": %d, \"height\": %d, \"channels\": [%s]}\n", W, H, names.c_str());
+        fflush(stdout);
+        _Exit(0);
+    }
+
     // ---- debug mode: `dumpscene_ref scene.pbrt --path x y sampleIndex` prints, for one pixel sample, the
     // radiance the reference's PathIntegrator::Li returns when maxDepth is cut at 0, 1, 2, ... (the
     // increments are the per-vertex contributions), to localise a divergence of our kernels.
@@ -244,18 +282,28 @@ int main(int argc, char **argv) {
     w.f32("camera_params", {2}, {pc->lensRadius, pc->focalDistance});
 
     // ---- film (RGBFilm) and its sensor
-    if (!film.Is<RGBFilm>()) die("only the rgb film is dumped so far");
-    const RGBFilm *rf = film.Cast<RGBFilm>();
-    Bounds2i pb = rf->pixelBounds;
-    w.i32("film_ints", {6}, {pb.pMin.x, pb.pMin.y, pb.pMax.x, pb.pMax.y, rf->fullResolution.x, rf->fullResolution.y});
-    if (!rf->filter.Is<BoxFilter>()) die("only the box filter is dumped so far");
-    Vector2f fr = rf->filter.Radius();
-    w.f32("film_params", {4}, {fr.x, fr.y, rf->sensor->imagingRatio, rf->maxComponentValue});
-    std::vector<float> om(9);
-    for (int i = 0; i < 9; ++i) om[i] = rf->outputRGBFromSensorRGB[i / 3][i % 3];
-    w.f32("film_matrix", {9}, om);
-    int sr = pool.add(&rf->sensor->r_bar, 0), sg = pool.add(&rf->sensor->g_bar, 0), sb = pool.add(&rf->sensor->b_bar, 0);
-    w.i32("film_sensor", {3}, {sr, sg, sb});
+    auto dumpFilm = [&](const auto *rf) {
+        Bounds2i pb = rf->pixelBounds;
+        w.i32("film_ints", {6}, {pb.pMin.x, pb.pMin.y, pb.pMax.x, pb.pMax.y, rf->fullResolution.x, rf->fullResolution.y});
+        if (!rf->filter.template Is<BoxFilter>()) die("only the box filter is dumped so far");
+        Vector2f fr = rf->filter.Radius();
+        w.f32("film_params", {4}, {fr.x, fr.y, rf->sensor->imagingRatio, rf->maxComponentValue});
+        std::vector<float> om(9);
+        for (int i = 0; i < 9; ++i) om[i] = rf->outputRGBFromSensorRGB[i / 3][i % 3];
+        w.f32("film_matrix", {9}, om);
+        int sr = pool.add(&rf->sensor->r_bar, 0), sg = pool.add(&rf->sensor->g_bar, 0), sb = pool.add(&rf->sensor->b_bar, 0);
+        w.i32("film_sensor", {3}, {sr, sg, sb});
+    };
+    if (film.Is<RGBFilm>()) {
+        w.u32("film_type", {1}, {0});
+        dumpFilm(film.Cast<RGBFilm>());
+    } else if (film.Is<SpectralFilm>()) {  // film.h:430-560
+        const SpectralFilm *sf = film.Cast<SpectralFilm>();
+        w.u32("film_type", {1}, {1});
+        dumpFilm(sf);
+        w.f32("film_spectral", {3}, {float(sf->nBuckets), sf->lambdaMin, sf->lambdaMax});
+    } else
+        die("only the rgb and spectral films are dumped so far");
 
     // ---- sampler
     if (sampler.Is<ZSobolSampler>()) {

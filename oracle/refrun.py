@@ -109,3 +109,25 @@ def dump_scene(pbrt_file, out_b2rs, bvh=True):
     if r.returncode != 0:
         raise RuntimeError(f"dumpscene_ref failed ({r.returncode}): {r.stderr[-2000:]}")
     return out_b2rs
+
+
+def render_channels(pbrt_file):
+    """The reference's render loop + Film::GetImage through dumpscene_ref --render: every channel of the
+    film's image as (H, W, C) float32, and the channel names.  For films the oracle build has no file
+    writer for (the spectral film's EXR)."""
+    import time
+    out = pbrt_file + ".img.b2rs"
+    t = time.time()
+    r = subprocess.run([DUMPSCENE, pbrt_file, "--render", out], capture_output=True, text=True,
+                       cwd=os.path.dirname(pbrt_file))
+    dt = time.time() - t
+    if r.returncode != 0:
+        raise RuntimeError(f"dumpscene_ref --render failed ({r.returncode}): {r.stderr[-2000:]}")
+    info = json.loads([l for l in r.stdout.strip().splitlines() if l.startswith("{")][-1])
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("b2_scenes", os.path.join(os.path.dirname(HERE), "pbrt-v4_b200", "scenes.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    img = mod.load_b2rs(out)["image"]
+    os.unlink(out)
+    return np.ascontiguousarray(img, np.float32), info["channels"], dt

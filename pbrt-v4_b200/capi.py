@@ -150,7 +150,8 @@ class RenderDesc(C.Structure):
                 ("n_lights", C.c_uint32), ("n_meshes", C.c_uint32), ("spectra", C.POINTER(Spectrum)),
                 ("materials", C.POINTER(Material)), ("lights", C.POINTER(Light)), ("meshes", C.POINTER(MeshAttr)),
                 ("n_light_bvh_nodes", C.c_uint32), ("light_bvh_bounds", C.c_float * 6),
-                ("light_bvh_nodes", C.c_void_p), ("light_bit_trails", C.POINTER(C.c_uint32))]
+                ("light_bvh_nodes", C.c_void_p), ("light_bit_trails", C.POINTER(C.c_uint32)),
+                ("n_buckets", C.c_uint32), ("lambda_min", C.c_float), ("lambda_max", C.c_float)]
 
 
 class RenderStats(C.Structure):
@@ -166,5 +167,6 @@ SYMBOLS.update({
     "b200pt_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "b200pt_film_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "b200pt_film_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "b200pt_film_spectral_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "b200pt_render_get_stats": (C.c_int, [C.c_void_p, C.POINTER(RenderStats)]),
 })

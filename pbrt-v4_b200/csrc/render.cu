@@ -272,6 +272,36 @@ __global__ void FilmAddKernel(PassBuffers pb, int nPixels, int nSamplesInPass, d
     dst[1] = b;
 }
 
+// Spectral film: after the RGB sums, each sample's 31 wavelengths go to their buckets (planes of n pixels,
+// so neighbouring pixels' accesses to one bucket share sectors); same order as the CPU film: samples of a
+// pixel in index order, wavelengths in order.
+__global__ void FilmAddSpectralKernel(FilmDev fd, PassBuffers pb, int nPixels, int nSamplesInPass, double *film) {
+    int pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= nPixels) return;
+    double *bucketSums = film + 4ll * nPixels + pix;
+    double *weightSums = bucketSums + (long long)fd.nBuckets * nPixels;
+    const long long n = pb.n;
+    for (int s = 0; s < nSamplesInPass; ++s) {
+        long long path = (long long)s * nPixels + pix;
+        const float *L = pb.L + path;
+        SpectralFilmAdd(fd, pb.scalars[path], 1.f, [&](int k) { return L[k * n]; },
+                        [&](int b, float v, float w) {
+                            bucketSums[(long long)b * nPixels] += v;
+                            weightSums[(long long)b * nPixels] += w;
+                        });
+    }
+}
+
+// SpectralFilm::GetImage's spectral channels (film.cpp:1262-1272): bucketSums / weightSums in double, to float
+__global__ void FilmSpectralImageKernel(int nBuckets, const double *acc, int nPixels, float *out) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= (long long)nPixels * nBuckets) return;
+    int pix = (int)(i / nBuckets), b = (int)(i % nBuckets);
+    double sum = acc[4ll * nPixels + (long long)b * nPixels + pix];
+    double w = acc[4ll * nPixels + (long long)(nBuckets + b) * nPixels + pix];
+    out[i] = w > 0 ? (float)(sum / w) : 0.f;
+}
+
 // RGBFilm::GetPixelRGB (film.h:261-277)
 __global__ void FilmImageKernel(FilmDev film, const double *acc, int nPixels, float *rgb) {
     int pix = blockIdx.x * blockDim.x + threadIdx.x;
@@ -341,6 +371,17 @@ cudaError_t LaunchFinish(const RenderSceneDev &rs, const PassBuffers &pb, int nA
 }
 cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream) {
     FilmAddKernel<<<Blocks(nPixels, 128), 128, 0, stream>>>(pb, nPixels, nSamplesInPass, film);
+    return cudaGetLastError();
+}
+cudaError_t LaunchFilmAddSpectral(const FilmDev &film, const PassBuffers &pb, int nPixels, int nSamplesInPass,
+                                  double *acc, cudaStream_t stream) {
+    FilmAddSpectralKernel<<<Blocks(nPixels, 128), 128, 0, stream>>>(film, pb, nPixels, nSamplesInPass, acc);
+    return cudaGetLastError();
+}
+cudaError_t LaunchFilmSpectralImage(const FilmDev &film, const double *acc, int nPixels, float *out,
+                                    cudaStream_t stream) {
+    long long n = (long long)nPixels * film.nBuckets;
+    FilmSpectralImageKernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(film.nBuckets, acc, nPixels, out);
     return cudaGetLastError();
 }
 cudaError_t LaunchFilmImage(const FilmDev &film, const double *acc, int nPixels, float *rgb, cudaStream_t stream) {

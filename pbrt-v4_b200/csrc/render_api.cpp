@@ -32,6 +32,7 @@ struct b200pt_render {
     unsigned long long *dCounters = nullptr;  // [0] closest rays, [1] shadow rays
     int *dRayCounter = nullptr;               // work counter of the persistent traversal kernel
     int nPixels = 0;
+    size_t filmDoubles = 0;  // 4 per pixel, + 2 * nBuckets per pixel for a spectral film
     long long maxPathsPerPass = 4ll << 20;    // B200PT_PASS_PATHS overrides
     b200pt_render_stats stats{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -115,11 +116,12 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         if (m.material < 0) r->matMask |= 1u;  // null materials go through the diffuse queue, which ends the path
     if (r->matMask == 0) r->matMask = 1;
     if (const char *v = getenv("B200PT_PASS_PATHS")) r->maxPathsPerPass = std::max(1ll, atoll(v));
-    if (cudaMalloc((void **)&r->dFilm, sizeof(double) * 4 * r->nPixels) != cudaSuccess ||
-        cudaMalloc((void **)&r->dImage, sizeof(float) * 3 * r->nPixels) != cudaSuccess ||
+    r->filmDoubles = size_t(r->nPixels) * (4 + 2 * size_t(r->dev.film.nBuckets));
+    if (cudaMalloc((void **)&r->dFilm, sizeof(double) * r->filmDoubles) != cudaSuccess ||
+        cudaMalloc((void **)&r->dImage, sizeof(float) * std::max(3, r->dev.film.nBuckets) * size_t(r->nPixels)) != cudaSuccess ||
         cudaMalloc((void **)&r->dCounters, 4 * sizeof(unsigned long long)) != cudaSuccess ||
         cudaEventCreate(&r->ev0) != cudaSuccess || cudaEventCreate(&r->ev1) != cudaSuccess ||
-        cudaMemsetAsync(r->dFilm, 0, sizeof(double) * 4 * r->nPixels, ctx->stream) != cudaSuccess ||
+        cudaMemsetAsync(r->dFilm, 0, sizeof(double) * r->filmDoubles, ctx->stream) != cudaSuccess ||
         cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
         ctx->err = std::string("render setup: ") + cudaGetErrorString(cudaGetLastError());
         return fail(B200PT_ERR_CUDA);
@@ -133,7 +135,7 @@ int b200pt_film_clear(b200pt_render *r) {
     if (!r) return B200PT_ERR_INVALID;
     b200pt_ctx *ctx = r->scene->ctx;
     B2_CUDA(ctx, cudaSetDevice(ctx->device));
-    B2_CUDA(ctx, cudaMemsetAsync(r->dFilm, 0, sizeof(double) * 4 * r->nPixels, ctx->stream));
+    B2_CUDA(ctx, cudaMemsetAsync(r->dFilm, 0, sizeof(double) * r->filmDoubles, ctx->stream));
     return B200PT_OK;
 }
 
@@ -202,6 +204,10 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
         }
         B2_CUDA(ctx, LaunchFinish(r->dev, pb, nActive, ctx->stream));
         B2_CUDA(ctx, LaunchFilmAdd(pb, nPix, ns, r->dFilm, ctx->stream));
+        if (r->dev.film.type == 1) {
+            B2_CUDA(ctx, LaunchFilmAddSpectral(r->dev.film, pb, nPix, ns, r->dFilm, ctx->stream));
+            ++launches;
+        }
         B2_CUDA(ctx, LaunchSumCounts(pb, maxDepth + 1, r->dCounters, ctx->stream));
         launches += 3;
     }
@@ -215,7 +221,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
 int b200pt_film_device_ptr(b200pt_render *r, void **ptr, uint64_t *n_doubles) {
     if (!r || !ptr) return B200PT_ERR_INVALID;
     *ptr = r->dFilm;
-    if (n_doubles) *n_doubles = 4ull * r->nPixels;
+    if (n_doubles) *n_doubles = r->filmDoubles;
     return B200PT_OK;
 }
 
@@ -223,7 +229,7 @@ int b200pt_film_read(b200pt_render *r, double *rgb_weight) {
     if (!r || !rgb_weight) return B200PT_ERR_INVALID;
     b200pt_ctx *ctx = r->scene->ctx;
     B2_CUDA(ctx, cudaSetDevice(ctx->device));
-    B2_CUDA(ctx, cudaMemcpyAsync(rgb_weight, r->dFilm, sizeof(double) * 4 * r->nPixels, cudaMemcpyDeviceToHost,
+    B2_CUDA(ctx, cudaMemcpyAsync(rgb_weight, r->dFilm, sizeof(double) * r->filmDoubles, cudaMemcpyDeviceToHost,
                                  ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200PT_OK;
@@ -235,6 +241,21 @@ int b200pt_film_image(b200pt_render *r, float *rgb) {
     B2_CUDA(ctx, cudaSetDevice(ctx->device));
     B2_CUDA(ctx, LaunchFilmImage(r->dev.film, r->dFilm, r->nPixels, r->dImage, ctx->stream));
     B2_CUDA(ctx, cudaMemcpyAsync(rgb, r->dImage, sizeof(float) * 3 * r->nPixels, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200PT_OK;
+}
+
+int b200pt_film_spectral_image(b200pt_render *r, float *buckets) {
+    if (!r || !buckets) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    if (r->dev.film.type != 1) {
+        ctx->err = "b200pt_film_spectral_image: the film is not a spectral film";
+        return B200PT_ERR_INVALID;
+    }
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2_CUDA(ctx, LaunchFilmSpectralImage(r->dev.film, r->dFilm, r->nPixels, r->dImage, ctx->stream));
+    B2_CUDA(ctx, cudaMemcpyAsync(buckets, r->dImage, sizeof(float) * size_t(r->dev.film.nBuckets) * r->nPixels,
+                                 cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200PT_OK;
 }

@@ -26,7 +26,12 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     };
     if (!d) return bad("null render description");
     if (d->camera_type != 0) return bad("unsupported camera type");
-    if (d->film_type != 0) return bad("unsupported film type");
+    if (d->film_type > 1) return bad("unsupported film type");
+    if (d->film_type == 1) {
+        if (d->n_buckets < 1 || d->n_buckets > 64) return bad("spectral film: n_buckets must be 1..64");
+        if (d->lambda_min != 395.f || d->lambda_max != 705.f)
+            return bad("spectral film: lambda_min / lambda_max must be 395 / 705 nm (the build's sampled range)");
+    }
     if (d->sampler_type != 0) return bad("unsupported sampler type");
     if (d->light_sampler > 2) return bad("unsupported light sampler (uniform, power and bvh are implemented)");
     if (d->light_sampler == 2 && d->n_lights && (!d->light_bit_trails || (d->n_light_bvh_nodes && !d->light_bvh_nodes)))
@@ -48,7 +53,8 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     std::memcpy(rs.camera.renderFromCamera, d->render_from_camera, 64);
     rs.camera.lensRadius = d->lens_radius;
     rs.camera.focalDistance = d->focal_distance;
-    rs.film.type = 0;
+    rs.film.type = d->film_type;
+    rs.film.nBuckets = d->film_type == 1 ? int32_t(d->n_buckets) : 0;
     rs.film.x0 = d->pixel_bounds[0];
     rs.film.y0 = d->pixel_bounds[1];
     rs.film.x1 = d->pixel_bounds[2];

@@ -54,6 +54,11 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream);
 cudaError_t LaunchFinish(const RenderSceneDev &rs, const PassBuffers &pb, int nActive, cudaStream_t stream);
 cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream);
+// spectral film: the bucket planes behind the 4 * nPixels rgbw doubles of `film`
+cudaError_t LaunchFilmAddSpectral(const FilmDev &film, const PassBuffers &pb, int nPixels, int nSamplesInPass,
+                                  double *acc, cudaStream_t stream);
+cudaError_t LaunchFilmSpectralImage(const FilmDev &film, const double *acc, int nPixels, float *out,
+                                    cudaStream_t stream);
 cudaError_t LaunchFilmImage(const FilmDev &film, const double *acc, int nPixels, float *rgb, cudaStream_t stream);
 // sums counts over depths into totals[0] (closest rays) and totals[1] (shadow rays)
 cudaError_t LaunchSumCounts(const PassBuffers &pb, int depths, unsigned long long *totals, cudaStream_t stream);

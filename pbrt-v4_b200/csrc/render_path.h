@@ -482,4 +482,37 @@ B2_SPECTRAL_LOOP
     rgbw[3] = filterWeight;
 }
 
+// SpectralFilm::AddSample, the spectral half (film.h:466-488): L clamped as a whole to maxComponentValue,
+// times weight * CIE_Y_integral, each wavelength added to its bucket.  L is the sample's radiance as the
+// integrator returned it (after the NaN / Inf guard of cpu/integrators.cpp:270-279), NOT divided by the
+// wavelength pdf; after TerminateSecondary the secondary wavelengths are added too, as the reference does.
+// acc(bucket, value, weight) performs `bucketSums[b] += value; weightSums[b] += weight` in doubles.
+constexpr float kCIE_Y_integral = 106.856895f;  // util/spectrum.h:31
+B2_HD int LambdaToBucket(float lambda, int nBuckets) {  // film.h:534-539
+    int bucket = (int)(nBuckets * (lambda - kLambdaMin) / (kLambdaMax - kLambdaMin));
+    return bucket < 0 ? 0 : (bucket > nBuckets - 1 ? nBuckets - 1 : bucket);
+}
+template <class LFn, class Acc>
+B2_HD void SpectralFilmAdd(const FilmDev &film, float lambdaU, float weight, LFn L, Acc acc) {
+    bool bad = false;
+    float lm = L(0);
+B2_SPECTRAL_LOOP
+    for (int k = 0; k < kNLambda; ++k) {
+        float v = L(k);
+        bad |= std::isnan(v) | std::isinf(v);
+        lm = fmaxf(lm, v);
+    }
+    bool clamp = !bad && lm > film.maxComponentValue;
+    float sc = clamp ? film.maxComponentValue / lm : 1.f;
+    float wY = weight * kCIE_Y_integral;
+    LambdaIter li(lambdaU);
+B2_SPECTRAL_LOOP
+    for (int k = 0; k < kNLambda; ++k, li.Next()) {
+        float v = bad ? 0.f : L(k);
+        if (clamp) v *= sc;
+        v *= wY;
+        acc(LambdaToBucket(li.lam, film.nBuckets), v, weight);
+    }
+}
+
 }  // namespace b200pt

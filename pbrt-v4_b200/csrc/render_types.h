@@ -59,7 +59,8 @@ struct CameraDev {
 };
 
 struct FilmDev {
-    uint32_t type;               // 0 = RGBFilm (film.h:232-310)
+    uint32_t type;               // 0 = RGBFilm (film.h:232-310), 1 = SpectralFilm (film.h:430-560)
+    int32_t nBuckets;            // spectral film
     int32_t x0, y0, x1, y1;      // pixelBounds
     int32_t fullResX, fullResY;
     uint32_t filterType;         // 0 box

@@ -44,6 +44,12 @@ class RenderScene:
         return int(b[2] - b[0]), int(b[3] - b[1])
 
     @property
+    def n_buckets(self):
+        """Bands of a spectral film, 0 for an RGB film."""
+        d = self.d
+        return int(d["film_spectral"][0]) if "film_type" in d and int(d["film_type"][0]) == 1 else 0
+
+    @property
     def spp(self):
         return int(self.d["sampler"][1])
 
@@ -55,7 +61,10 @@ class RenderScene:
         r.camera_from_raster[:] = [float(x) for x in d["camera_from_raster"]]
         r.render_from_camera[:] = [float(x) for x in d["render_from_camera"]]
         r.lens_radius, r.focal_distance = float(d["camera_params"][0]), float(d["camera_params"][1])
-        r.film_type = 0
+        r.film_type = int(d["film_type"][0]) if "film_type" in d else 0
+        if r.film_type == 1:  # SpectralFilm
+            r.n_buckets = int(d["film_spectral"][0])
+            r.lambda_min, r.lambda_max = float(d["film_spectral"][1]), float(d["film_spectral"][2])
         r.pixel_bounds[:] = [int(x) for x in d["film_ints"][:4]]
         r.full_resolution[:] = [int(x) for x in d["film_ints"][4:6]]
         r.filter_radius[:] = [float(x) for x in d["film_params"][:2]]
@@ -149,8 +158,24 @@ class B200Renderer:
         capi.check(self._L.b200pt_film_clear(self._r), self.agg._ctx)
 
     def film(self):
-        out = np.empty((self.height, self.width, 4), dtype=np.float64)
-        capi.check(self._L.b200pt_film_read(self._r, out.ctypes.data_as(C.POINTER(C.c_double))), self.agg._ctx)
+        """{rgbSum[3], weightSum} per pixel as (H, W, 4) doubles."""
+        return self.film_all()[0]
+
+    def film_all(self):
+        """-> (rgbw (H, W, 4), bucketSums (nB, H, W), weightSums (nB, H, W)); the last two None for an RGB film."""
+        nb, n = self.rscene.n_buckets, self.height * self.width
+        buf = np.empty(n * (4 + 2 * nb), dtype=np.float64)
+        capi.check(self._L.b200pt_film_read(self._r, buf.ctypes.data_as(C.POINTER(C.c_double))), self.agg._ctx)
+        rgbw = buf[:4 * n].reshape(self.height, self.width, 4)
+        if not nb:
+            return rgbw, None, None
+        planes = buf[4 * n:].reshape(2, nb, self.height, self.width)
+        return rgbw, planes[0], planes[1]
+
+    def spectral_image(self):
+        """The S0.* channels of SpectralFilm::GetImage as (H, W, nB) float32."""
+        out = np.empty((self.height, self.width, self.rscene.n_buckets), dtype=np.float32)
+        capi.check(self._L.b200pt_film_spectral_image(self._r, out.ctypes.data_as(C.POINTER(C.c_float))), self.agg._ctx)
         return out
 
     def film_device_ptr(self):

@@ -10,6 +10,8 @@ File layout:  u32 magic 'B2SC', u32 version=1, u32 nMeshes, u32 nInstances
 from dataclasses import dataclass, field
 from typing import List
 
+import os
+
 import numpy as np
 
 MAGIC = 0x43533242
@@ -309,7 +311,8 @@ MATERIALS = {
 
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
-                 boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None):
+                 boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
+                 film="rgb", nbuckets=31):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -323,7 +326,11 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
         f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "{lightsampler}"'
         + (' "bool regularize" true' if regularize else ''),
         'PixelFilter "box"',
-        f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false',
+        (f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false'
+         if film == "rgb" else
+         # SpectralFilm (film.h:430-560) only accepts an .exr name; the oracle reads its Image out directly
+         f'Film "spectral" "string filename" "{os.path.splitext(out)[0]}.exr" "integer nbuckets" {nbuckets} '
+         f'"integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false'),
         'WorldBegin',
     ]
     if instanced:

@@ -79,17 +79,22 @@ def rendercheck(P):
                                "-fPIC", "-pthread", "-o", out] + src)
     L = C.CDLL(out)
 
-    def run(rscene, first=0, n=None, stride=1, threads=8, use_host_bvh=False):
+    def run(rscene, first=0, n=None, stride=1, threads=8, use_host_bvh=False, full=False):
         keep = []
         sd = P.render.scene_desc(rscene.geometry, rscene.bvh if use_host_bvh else None, keep)
         rd = rscene.desc(keep)
         w, h = rscene.resolution
-        film = np.zeros((h, w, 4), np.float64)
+        nb = rscene.n_buckets
+        film = np.zeros(h * w * (4 + 2 * nb), np.float64)
         msg = C.create_string_buffer(512)
         rc = L.rendercheck_run(C.byref(sd), C.byref(rd), int(first), int(rscene.spp if n is None else n),
                                int(stride), film.ctypes.data_as(C.POINTER(C.c_double)), msg, 512, threads)
         assert rc == 0, msg.value.decode()
-        return film
+        rgbw = film[:4 * h * w].reshape(h, w, 4)
+        if not full:
+            return rgbw
+        planes = film[4 * h * w:].reshape(2, nb, h, w)  # spectral film: bucketSums, weightSums
+        return rgbw, planes[0], planes[1]
     return run
 
 

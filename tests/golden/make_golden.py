@@ -60,6 +60,8 @@ RENDER_CASES = {
     "cornell_infinite_r64_s16": dict(res=64, spp=16, maxdepth=5, lightsampler="bvh", many_lights=20,
                                      infinite=(0.4, 0.5, 0.8)),
     "cornell_infinite_power_r48_s8": dict(res=48, spp=8, maxdepth=4, lightsampler="power", infinite=(0.4, 0.5, 0.8)),
+    # SpectralFilm, 31 bands (configs[3]'s film); the reference image has 3 + 31 channels
+    "cornell_spectral_r48_s16": dict(res=48, spp=16, maxdepth=5, film="spectral", nbuckets=31),
     "cornell_coated_r64_s16": dict(res=64, spp=16, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough")),
     "cornell_glass_r64_s16": dict(res=64, spp=16, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass")),
 }
@@ -91,7 +93,10 @@ def make_render_goldens(P, refrun, out):
         with tempfile.TemporaryDirectory() as tmp:
             pbrt, pfm = os.path.join(tmp, name + ".pbrt"), os.path.join(tmp, name + ".pfm")
             P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
-            img, secs = refrun.render(pbrt, pfm)
+            if kw.get("film") == "spectral":  # no EXR writer in the oracle build: Film::GetImage read directly
+                img, _, secs = refrun.render_channels(pbrt)
+            else:
+                img, secs = refrun.render(pbrt, pfm)
             refrun.dump_scene(pbrt, os.path.join(out, name + ".b2rs"))
             np.save(os.path.join(out, name + "_ref.npy"), img.astype(np.float32))
             if name in NOISE_GATED:

@@ -51,7 +51,8 @@ struct HostIO {
 
 }  // namespace
 
-// rgbw: 4 doubles per pixel (rgbSum, weightSum), row major.  Returns 0 or an error code; err text in msg.
+// rgbw: 4 doubles per pixel (rgbSum, weightSum), row major; a spectral film appends its bucket planes
+// (layout of b200pt_film_read).  Returns 0 or an error code; err text in msg.
 extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_desc *rd, int firstSample,
                                int nSamples, int stride, double *rgbw, char *msg, int msgLen, int nThreads) {
     HostScene hs;
@@ -98,6 +99,15 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
                         FinishPath(rs, p.lambdaU, p.flags, p.filterWeight, [&](int i) { return io.L[i]; }, out);
                         double *px = rgbw + 4 * (size_t(y) * W + x);
                         for (int c = 0; c < 4; ++c) px[c] += out[c];
+                        if (rs.film.type == 1) {  // spectral film: planes behind the rgbw block, as on the device
+                            size_t nPix = size_t(W) * H, pix = size_t(y) * W + x;
+                            double *bs = rgbw + 4 * nPix + pix, *ws = bs + size_t(rs.film.nBuckets) * nPix;
+                            SpectralFilmAdd(rs.film, p.lambdaU, p.filterWeight, [&](int i) { return io.L[i]; },
+                                            [&](int b, float v, float wt) {
+                                                bs[size_t(b) * nPix] += v;
+                                                ws[size_t(b) * nPix] += wt;
+                                            });
+                        }
                     }
         });
     for (auto &th : pool) th.join();

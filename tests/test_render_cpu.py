@@ -115,3 +115,20 @@ def test_fresh_reference_render(P, rendercheck, refrun, tmp_path, kw):
     img = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
     assert rrmse(img, ref) <= TOL_RRMSE
     assert abs(img.mean() - ref.mean()) <= TOL_MEAN * ref.mean()
+
+
+def test_golden_image_spectral_film(P, rendercheck):
+    """SpectralFilm (film.h:430-560): RGB channels as the RGB film's, and the 31 bucket channels
+    bucketSums / weightSums against the reference's Film::GetImage (dumpscene_ref --render)."""
+    name = "cornell_spectral_r48_s16"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    assert rsc.n_buckets == 31 and ref.shape[2] == 34
+    rgbw, bsum, wsum = rendercheck(rsc, full=True)
+    img = P.render.film_to_image(rgbw, rsc.d["film_matrix"])
+    assert rrmse(img, ref[..., :3]) <= TOL_RRMSE
+    spec = np.where(wsum > 0, bsum / np.where(wsum > 0, wsum, 1), 0).astype(np.float32).transpose(1, 2, 0)
+    assert rrmse(spec, ref[..., 3:]) <= TOL_RRMSE
+    assert abs(spec.mean() - ref[..., 3:].mean()) <= TOL_MEAN * ref[..., 3:].mean()
+    # every sample put each of its 31 wavelengths into some bucket with weight 1
+    np.testing.assert_array_equal(wsum.sum(axis=0), 31.0 * rsc.spp)

@@ -142,3 +142,37 @@ def test_full_size_config1(P, refrun, tmp_path):
         r.close()
     assert rrmse(img, ref) <= TOL_RRMSE
     assert abs(img.mean() - ref.mean()) <= TOL_MEAN * ref.mean()
+
+
+def test_spectral_film(P):
+    """SpectralFilm on the device: RGB and the 31 bucket channels against the reference's image; the bucket
+    planes read back equal the spectral image; weights are whole numbers of wavelengths."""
+    name = "cornell_spectral_r48_s16"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img, spec = r.image(), r.spectral_image()
+        rgbw, bsum, wsum = r.film_all()
+        ptr, nd = r.film_device_ptr()
+    finally:
+        r.close()
+    n = img.shape[0] * img.shape[1]
+    assert nd == n * (4 + 2 * 31) and spec.shape == ref[..., 3:].shape
+    assert rrmse(img, ref[..., :3]) <= TOL_RRMSE
+    assert rrmse(spec, ref[..., 3:]) <= TOL_RRMSE
+    assert abs(spec.mean() - ref[..., 3:].mean()) <= TOL_MEAN * ref[..., 3:].mean()
+    mine = np.where(wsum > 0, bsum / np.where(wsum > 0, wsum, 1), 0).astype(np.float32).transpose(1, 2, 0)
+    np.testing.assert_array_equal(mine, spec)
+    np.testing.assert_array_equal(wsum.sum(axis=0), 31.0 * rsc.spp)
+    np.testing.assert_array_equal(rgbw[..., 3], float(rsc.spp))
+
+
+def test_spectral_image_needs_a_spectral_film(P, cornell):
+    r = P.B200Renderer(cornell)
+    try:
+        with pytest.raises(P.capi.B200PTError):
+            r.spectral_image()
+    finally:
+        r.close()
