@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--render-cpu-spp", type=int, default=64, help="spp of the bounded pbrt_ref sample")
     ap.add_argument("--no-config3", action="store_true", help="skip the config-3 (10M instanced triangles) section")
     ap.add_argument("--config3-spp", type=int, default=32, help="spp of config 3's frame rendered per step")
+    ap.add_argument("--no-config4", action="store_true", help="skip the config-4 (realistic lens + spectral film) section")
+    ap.add_argument("--config4-spp", type=int, default=64, help="spp of config 4's frame rendered per step")
+    ap.add_argument("--config4-cpu-spp", type=int, default=4, help="spp of the bounded reference sample of config 4")
     ap.add_argument("--config3-cpu-spp", type=int, default=2, help="spp of the bounded pbrt_ref sample of config 3")
     return ap.parse_args()
 
@@ -388,6 +391,87 @@ def config3_cpu_reference(args, P):
                       f"clock of the whole pbrt_ref process incl. parse + BVH builds"}
 
 
+CONFIG4_CASE = "config4_full"  # BASELINE.json configs[3]; tables in tests/golden (make_golden.py CONFIG4_FULL)
+
+
+def config4_section(args, P, torch, dist, rank, world, local, stream, barrier):
+    """Config 4 end to end: RealisticCamera rays through the lens table, path tracing, 31-band SpectralFilm;
+    --config4-spp of its 256 spp per step, sample stripes over the ranks, the whole film (RGB sums + 2 x 31
+    bucket planes, fp64) reduced by NCCL, the spectral image read back on rank 0."""
+    rsc = P.RenderScene.load(os.path.join(ROOT, "tests", "golden", CONFIG4_CASE + ".b2rs"))
+    spp = min(args.config4_spp, rsc.spp)
+    r = P.B200Renderer(rsc, device=local, stream=stream.cuda_stream)
+    ptr, nd = r.film_device_ptr()
+    film_t = torch.as_tensor(_DevArray(ptr, nd, "<f8"), device="cuda")
+
+    def frame(read):
+        r.clear()
+        r.render(*P.parallel.sample_stripe(spp, rank, world))
+        P.parallel.reduce_film(film_t, dist)
+        return r.spectral_image() if (read and rank == 0) else None
+
+    for _ in range(min(args.warmup, 3)):
+        frame(False)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        frame(False)
+    e1.record(stream)
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    st = r.stats()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        img = frame(True)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    r.close()
+    t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_s = (float(x) for x in t.cpu())
+    if rank != 0:
+        return None
+    w, h = rsc.resolution
+    ns = w * h * spp * args.steps
+    out = {"metric": "render_msamples_per_s", "unit": "Msamples/s", "value": ns / (dev_ms * 1e-3) * 1e-6,
+           "ms_per_frame": dev_ms / args.steps, "scaling": "strong",
+           "workload": f"config4: Cornell room + 24-patch spectral chart, realistic camera ({len(rsc.d['camera_lens'])} lens "
+                       f"interfaces, double-Gauss 50 mm), spectral film {rsc.n_buckets} bands, {w}x{h}; {spp} of the frame's "
+                       f"{rsc.spp} spp per step, path maxdepth 5; sample stripes over {world} rank(s), film reduced by NCCL",
+           "e2e": {"value": ns / e2e_s * 1e-6, "unit": "Msamples/s", "h2d_bytes_per_step": 0,
+                   "d2h_bytes_per_step": w * h * 4 * rsc.n_buckets},
+           "film_bytes_reduced": nd * 8,
+           "rays_per_frame": (st["closest_rays"] + st["shadow_rays"]) * world,
+           "launches_per_frame": st["kernel_launches"], "image_mean": float(img.mean())}
+    if not args.no_cpu_baseline:
+        out["cpu_baseline"] = config4_cpu_reference(args, P)
+    return out
+
+
+def config4_cpu_reference(args, P):
+    """The reference's render loop + Film::GetImage (dumpscene_ref --render: the oracle build has no EXR writer,
+    which pbrt_ref's spectral film would need) on a bounded sample of config 4: the whole frame at
+    --config4-cpu-spp samples per pixel, all host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refrun
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    if not refrun.render_available():
+        return {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    import make_golden
+    kw = dict(make_golden.CONFIG4_FULL, spp=args.config4_cpu_spp)
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt = os.path.join(tmp, "c4.pbrt")
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), **kw)
+        _, _, secs = refrun.render_channels(pbrt)
+    n = kw["res"] * kw["res"] * kw["spp"]
+    return {"value": n / secs * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
+            "seconds": secs,
+            "sample": f"the config-4 scene at {kw['res']}x{kw['res']}, {kw['spp']} spp (config 4 is 256 spp), wall clock of "
+                      f"the whole process incl. parse and the camera's exit-pupil table (64 x 2^20 lens traces)"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU BVHAggregate on all host cores, bounded sample per step."""
     if rank != 0:
@@ -534,6 +618,13 @@ def main():
         del d_prim, d_shad, d_hits, d_occ
         config3 = config3_section(args, P, torch, dist, rank, world, local, stream, barrier)
 
+    config4 = None
+    if not args.no_config4:
+        if agg is not None:
+            agg.close()
+            agg = None
+        config4 = config4_section(args, P, torch, dist, rank, world, local, stream, barrier)
+
     # ---- max over ranks
     t = torch.tensor([total_ms, e2e_s, ms_closest, ms_any], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -563,6 +654,7 @@ def main():
             "gpu_launches": 2 * args.steps,
             "render": render,
             "config3": config3,
+            "config4": config4,
             "clocks": clk,
             "scene": {"bvh2_nodes": st["n_bvh2_nodes"], "wide_nodes": st["n_wide_nodes"],
                       "device_bytes": st["device_bytes"], "build_s": st["build_seconds"]},

@@ -207,7 +207,7 @@ typedef struct b200pt_mesh_attr {
 } b200pt_mesh_attr;
 
 typedef struct b200pt_render_desc {
-    /* camera: perspective (cameras.cpp:433-456) */
+    /* camera: 0 = perspective (cameras.cpp:433-456), 1 = realistic (fields at the end of this struct) */
     uint32_t camera_type;
     float camera_from_raster[16];
     float render_from_camera[16];
@@ -248,6 +248,19 @@ typedef struct b200pt_render_desc {
      * (the ISET 31-band setting); 1 <= n_buckets <= 64. */
     uint32_t n_buckets;
     float lambda_min, lambda_max;
+    /* camera_type 1 = RealisticCamera (cameras.cpp:820-884 TraceLensesFromFilm, :968-1019 SampleExitPupil /
+     * GenerateRay).  The host keeps the constructor's work (cameras.cpp:770-817: lens file, FocusThickLens,
+     * BoundExitPupil) and hands over: lens_elements = n x {curvatureRadius, thickness, eta, apertureRadius} in
+     * metres, front element first (RealisticCamera::elementInterfaces; curvatureRadius 0 = the aperture stop);
+     * exit_pupil_bounds = n x {pMin.x, pMin.y, pMax.x, pMax.y} (exitPupilBounds); physical_extent likewise;
+     * film_diagonal = Film::Diagonal() in metres.  Aperture images are not supported (circular stops).
+     * camera_from_raster, lens_radius and focal_distance are ignored for this camera. */
+    uint32_t n_lens_elements;
+    const float *lens_elements;
+    uint32_t n_exit_pupil_bounds;
+    const float *exit_pupil_bounds;
+    float physical_extent[4];
+    float film_diagonal;
 } b200pt_render_desc;
 
 typedef struct b200pt_render b200pt_render;

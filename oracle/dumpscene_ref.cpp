@@ -273,13 +273,28 @@ int main(int argc, char **argv) {
     const bool dumpBvh = !(argc > 3 && std::string(argv[3]) == "--no-bvh");
     SpectraPool pool;
 
-    // ---- camera (perspective only for now)
-    if (!camera.Is<PerspectiveCamera>()) die("only the perspective camera is dumped so far");
-    const PerspectiveCamera *pc = camera.Cast<PerspectiveCamera>();
-    w.u32("camera_type", {1}, {0});
-    w.f32("camera_from_raster", {16}, Mat(pc->cameraFromRaster.GetMatrix()));
-    w.f32("render_from_camera", {16}, Mat(pc->cameraTransform.renderFromCamera.startTransform.GetMatrix()));
-    w.f32("camera_params", {2}, {pc->lensRadius, pc->focalDistance});
+    // ---- camera: perspective, or the RealisticCamera's lens table and exit-pupil bounds (cameras.h:599-603)
+    if (camera.Is<PerspectiveCamera>()) {
+        const PerspectiveCamera *pc = camera.Cast<PerspectiveCamera>();
+        w.u32("camera_type", {1}, {0});
+        w.f32("camera_from_raster", {16}, Mat(pc->cameraFromRaster.GetMatrix()));
+        w.f32("render_from_camera", {16}, Mat(pc->cameraTransform.renderFromCamera.startTransform.GetMatrix()));
+        w.f32("camera_params", {2}, {pc->lensRadius, pc->focalDistance});
+    } else if (camera.Is<RealisticCamera>()) {
+        const RealisticCamera *rc = camera.Cast<RealisticCamera>();
+        if (rc->apertureImage) die("aperture images are not dumped");
+        w.u32("camera_type", {1}, {1});
+        w.f32("render_from_camera", {16}, Mat(rc->cameraTransform.renderFromCamera.startTransform.GetMatrix()));
+        std::vector<float> lens, pupil;
+        for (const auto &e : rc->elementInterfaces)
+            lens.insert(lens.end(), {e.curvatureRadius, e.thickness, e.eta, e.apertureRadius});
+        for (const Bounds2f &b : rc->exitPupilBounds) pupil.insert(pupil.end(), {b.pMin.x, b.pMin.y, b.pMax.x, b.pMax.y});
+        w.f32("camera_lens", {uint32_t(lens.size() / 4), 4}, lens);
+        w.f32("camera_exit_pupil", {uint32_t(pupil.size() / 4), 4}, pupil);
+        const Bounds2f &pe = rc->physicalExtent;
+        w.f32("camera_extent", {5}, {pe.pMin.x, pe.pMin.y, pe.pMax.x, pe.pMax.y, film.Diagonal()});
+    } else
+        die("only the perspective and realistic cameras are dumped so far");
 
     // ---- film (RGBFilm) and its sensor
     auto dumpFilm = [&](const auto *rf) {

@@ -151,7 +151,10 @@ class RenderDesc(C.Structure):
                 ("materials", C.POINTER(Material)), ("lights", C.POINTER(Light)), ("meshes", C.POINTER(MeshAttr)),
                 ("n_light_bvh_nodes", C.c_uint32), ("light_bvh_bounds", C.c_float * 6),
                 ("light_bvh_nodes", C.c_void_p), ("light_bit_trails", C.POINTER(C.c_uint32)),
-                ("n_buckets", C.c_uint32), ("lambda_min", C.c_float), ("lambda_max", C.c_float)]
+                ("n_buckets", C.c_uint32), ("lambda_min", C.c_float), ("lambda_max", C.c_float),
+                ("n_lens_elements", C.c_uint32), ("lens_elements", C.POINTER(C.c_float)),
+                ("n_exit_pupil_bounds", C.c_uint32), ("exit_pupil_bounds", C.POINTER(C.c_float)),
+                ("physical_extent", C.c_float * 4), ("film_diagonal", C.c_float)]
 
 
 class RenderStats(C.Structure):

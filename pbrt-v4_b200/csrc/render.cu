@@ -149,6 +149,9 @@ GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nA
         pb.L[k * n + i] = 0.f;
     }
     StoreHeader(pb, i, p);
+    pb.scalars[kCameraWeightScalar * n + i] = p.cameraWeight;
+    // a sample without a camera ray (vignetted by the lens system) keeps its queue slot with a ray that
+    // hits nothing (tMax < 0); the classify kernel drops it
     StoreRay(pb.rays[0], i, p.rayO, p.rayD, p.rayTMax);
     pb.rayPath[0][i] = i;
 }
@@ -161,7 +164,7 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
     if (t >= counts[0]) return;
     uint32_t slot = pb.hits[6ll * t];
     if (slot == kMissTag) {  // escaped: infinite lights add their radiance, the path ends
-        if (rs.nInfiniteLights) {
+        if (rs.nInfiniteLights && pb.rays[depth & 1][7ll * t + 6] >= 0) {
             struct {
                 const PassBuffers &pb;
                 int path;
@@ -250,7 +253,8 @@ FinishKernel(RenderSceneDev rs, PassBuffers pb, int nActive) {
     const long long n = pb.n;
     const float *L = pb.L + i;
     float rgbw[4];
-    FinishPath(rs, pb.scalars[i], (uint32_t)pb.ints[3 * n + i], 1.f, [&](int k) { return L[k * n]; }, rgbw);
+    const float cw = pb.scalars[kCameraWeightScalar * n + i];
+    FinishPath(rs, pb.scalars[i], (uint32_t)pb.ints[3 * n + i], 1.f, [&](int k) { return cw * L[k * n]; }, rgbw);
     reinterpret_cast<float4 *>(pb.rgbw)[i] = make_float4(rgbw[0], rgbw[1], rgbw[2], rgbw[3]);
 }
 
@@ -284,7 +288,8 @@ __global__ void FilmAddSpectralKernel(FilmDev fd, PassBuffers pb, int nPixels, i
     for (int s = 0; s < nSamplesInPass; ++s) {
         long long path = (long long)s * nPixels + pix;
         const float *L = pb.L + path;
-        SpectralFilmAdd(fd, pb.scalars[path], 1.f, [&](int k) { return L[k * n]; },
+        const float cw = pb.scalars[kCameraWeightScalar * n + path];
+        SpectralFilmAdd(fd, pb.scalars[path], 1.f, [&](int k) { return cw * L[k * n]; },
                         [&](int b, float v, float w) {
                             bucketSums[(long long)b * nPixels] += v;
                             weightSums[(long long)b * nPixels] += w;

@@ -23,6 +23,7 @@ struct b200pt_render {
     RenderSceneDev dev{};
     void *dSpectra = nullptr, *dMaterials = nullptr, *dLights = nullptr, *dMeshes = nullptr;
     void *dLightBvh = nullptr, *dBitTrails = nullptr, *dInfinite = nullptr;
+    void *dLens = nullptr, *dPupil = nullptr;
     double *dFilm = nullptr;
     float *dImage = nullptr;
     void *dPaths = nullptr;
@@ -64,6 +65,8 @@ int b200pt_render_destroy(b200pt_render *r) {
     cudaFree(r->dLightBvh);
     cudaFree(r->dBitTrails);
     cudaFree(r->dInfinite);
+    cudaFree(r->dLens);
+    cudaFree(r->dPupil);
     cudaFree(r->dFilm);
     cudaFree(r->dImage);
     cudaFree(r->dPaths);
@@ -98,7 +101,8 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         (rc = Upload(ctx, r->host.lights, &r->dLights)) || (rc = Upload(ctx, r->host.meshes, &r->dMeshes)) ||
         (rc = Upload(ctx, r->host.lightBvhNodes, &r->dLightBvh)) ||
         (rc = Upload(ctx, r->host.lightBitTrails, &r->dBitTrails)) ||
-        (rc = Upload(ctx, r->host.infiniteLights, &r->dInfinite)))
+        (rc = Upload(ctx, r->host.infiniteLights, &r->dInfinite)) || (rc = Upload(ctx, r->host.lens, &r->dLens)) ||
+        (rc = Upload(ctx, r->host.pupilBounds, &r->dPupil)))
         return fail(rc);
     r->nPixels = r->host.width * r->host.height;
     r->dev = r->host.rs;
@@ -109,6 +113,8 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     r->dev.lightBvhNodes = r->dLightBvh;
     r->dev.lightBitTrails = (const uint32_t *)r->dBitTrails;
     r->dev.infiniteLights = (const int32_t *)r->dInfinite;
+    r->dev.camera.lens = (const float *)r->dLens;
+    r->dev.camera.pupilBounds = (const float *)r->dPupil;
     r->dev.prims = scene->dev.prims;
     r->dev.instances = scene->dev.instances;
     for (const MaterialDev &m : r->host.materials) r->matMask |= 1u << m.type;

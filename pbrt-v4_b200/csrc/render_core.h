@@ -189,8 +189,26 @@ B2_HD void GeneratePerspectiveRay(const CameraDev &c, float pFilmX, float pFilmY
         ro = mk(lx, ly, 0);
         rd = Normalize(pFocus - ro);
     }
+    // RenderFromCamera(ray) = Transform::operator()(Ray) (util/transform.h:336-348): with an exact origin the
+    // error box is gamma(3) * sum |m_ij o_j| + |m_i3|; a pinhole at the render-space origin has none.
     o = XformPoint(c.renderFromCamera, ro);
     d = XformVector(c.renderFromCamera, rd);
+    const float *m = c.renderFromCamera;
+    if (ro.x != 0 || ro.y != 0 || ro.z != 0 || m[3] != 0 || m[7] != 0 || m[11] != 0) {
+        const float g3 = GammaF(3);
+        V3 e = mk(g3 * (fabsf(m[0] * ro.x) + fabsf(m[1] * ro.y) + fabsf(m[2] * ro.z) + fabsf(m[3])),
+                  g3 * (fabsf(m[4] * ro.x) + fabsf(m[5] * ro.y) + fabsf(m[6] * ro.z) + fabsf(m[7])),
+                  g3 * (fabsf(m[8] * ro.x) + fabsf(m[9] * ro.y) + fabsf(m[10] * ro.z) + fabsf(m[11])));
+        P3i pi = MakeP3i(o, e);
+        float lengthSquared = LengthSquared(d);
+        if (lengthSquared > 0) {
+            float dt = Dot(Abs(d), Err(pi)) / lengthSquared;
+            V3 s = d * dt;
+            pi.lo = mk(NextDown(pi.lo.x + s.x), NextDown(pi.lo.y + s.y), NextDown(pi.lo.z + s.z));
+            pi.hi = mk(NextUp(pi.hi.x + s.x), NextUp(pi.hi.y + s.y), NextUp(pi.hi.z + s.z));
+        }
+        o = Mid(pi);
+    }
 }
 
 }  // namespace b200pt

@@ -25,7 +25,16 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         return B200PT_ERR_INVALID;
     };
     if (!d) return bad("null render description");
-    if (d->camera_type != 0) return bad("unsupported camera type");
+    if (d->camera_type > 1) return bad("unsupported camera type (0 perspective, 1 realistic)");
+    if (d->camera_type == 1) {
+        if (d->n_lens_elements < 1 || d->n_lens_elements > 64 || !d->lens_elements)
+            return bad("realistic camera: 1..64 lens elements needed");
+        if (d->n_exit_pupil_bounds < 1 || !d->exit_pupil_bounds) return bad("realistic camera: exit pupil bounds missing");
+        if (!(d->film_diagonal > 0)) return bad("realistic camera: film diagonal must be positive");
+        for (uint32_t i = 0; i < d->n_lens_elements; ++i)
+            if (d->lens_elements[4 * i] != 0 && d->lens_elements[4 * i + 2] == 0)
+                return bad("realistic camera: a curved element with eta 0");
+    }
     if (d->film_type > 1) return bad("unsupported film type");
     if (d->film_type == 1) {
         if (d->n_buckets < 1 || d->n_buckets > 64) return bad("spectral film: n_buckets must be 1..64");
@@ -48,7 +57,17 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         if (!specOk(d->sensor_spectrum[c])) return bad("sensor spectrum index out of range");
 
     RenderSceneDev &rs = out.rs;
-    rs.camera.type = 0;
+    rs.camera.type = d->camera_type;
+    rs.camera.lens = rs.camera.pupilBounds = nullptr;
+    rs.camera.nLens = rs.camera.nPupilBounds = 0;
+    if (d->camera_type == 1) {
+        out.lens.assign(d->lens_elements, d->lens_elements + 4 * size_t(d->n_lens_elements));
+        out.pupilBounds.assign(d->exit_pupil_bounds, d->exit_pupil_bounds + 4 * size_t(d->n_exit_pupil_bounds));
+        rs.camera.nLens = int32_t(d->n_lens_elements);
+        rs.camera.nPupilBounds = int32_t(d->n_exit_pupil_bounds);
+        std::memcpy(rs.camera.physicalExtent, d->physical_extent, 16);
+        rs.camera.filmDiagonal = d->film_diagonal;
+    }
     std::memcpy(rs.camera.cameraFromRaster, d->camera_from_raster, 64);
     std::memcpy(rs.camera.renderFromCamera, d->render_from_camera, 64);
     rs.camera.lensRadius = d->lens_radius;

@@ -19,6 +19,7 @@ struct RenderHost {
     std::vector<uint32_t> lightBvhNodes;   // 8 per node
     std::vector<uint32_t> lightBitTrails;  // per light
     std::vector<int32_t> infiniteLights;   // light indices
+    std::vector<float> lens, pupilBounds;  // realistic camera: 4 floats per element / per film-radius bin
     int width = 0, height = 0;
 };
 

@@ -8,7 +8,8 @@
 
 namespace b200pt {
 
-constexpr int kPathScalars = 15;  // lambdaU, etaScale, pB, prev{pi.lo, pi.hi, n, ns}
+constexpr int kPathScalars = 16;  // lambdaU, etaScale, pB, prev{pi.lo, pi.hi, n, ns}, cameraWeight
+constexpr int kCameraWeightScalar = 15;  // written by the generate kernel, read when the sample is finished
 constexpr int kPathInts = 4;      // sampleIndex, dimension, depth, flags
 constexpr int kMatQueues = 4;     // one shading queue per MaterialType
 constexpr int kCountStride = 8;   // ints per depth in PassBuffers::counts

@@ -14,6 +14,7 @@
 // kernel ~20 K instructions and instruction-fetch bound (profiles/r01_render_v2_*).
 #pragma once
 #include "render_bsdf.h"
+#include "render_camera.h"
 #include "render_layered.h"
 #include "render_lightbvh.h"
 
@@ -35,6 +36,7 @@ struct PathRegs {
     int px, py, sampleIndex, dimension, depth;
     uint32_t flags;
     float etaScale, pB, filterWeight;
+    float cameraWeight;  // CameraRay::weight: L = weight * Li (cpu/integrators.cpp:247-252); 0 = no ray
     LightCtx prev;
     V3 rayO, rayD;
     float rayTMax;
@@ -75,10 +77,19 @@ B2_HD void GenerateCameraPath(const RenderSceneDev &rs, PathRegs &p, int px, int
     float l0, l1;
     ZSobolGet2D(s, l0, l1);
     p.dimension = s.dimension;
-    GeneratePerspectiveRay(rs.camera, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
+    p.cameraWeight = 1.f;
+    if (rs.camera.type == 1)
+        p.cameraWeight = GenerateRealisticRay(rs.camera, rs.film, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
+    else
+        GeneratePerspectiveRay(rs.camera, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
     p.rayTMax = INFINITY;
     p.depth = 0;
     p.flags = PF_ALIVE;
+    if (p.cameraWeight == 0) {  // no camera ray: the sample is added to the film with L = 0
+        p.flags = 0;
+        p.rayO = p.rayD = mk(0, 0, 0);
+        p.rayTMax = -1.f;
+    }
     p.etaScale = 1.f;
     p.pB = 0.f;
     p.prev.pi.lo = p.prev.pi.hi = p.prev.n = p.prev.ns = mk(0, 0, 0);

@@ -52,10 +52,17 @@ struct MeshAttrDev {
 };
 
 struct CameraDev {
-    uint32_t type;               // 0 perspective (cameras.cpp:433-456)
+    uint32_t type;               // 0 perspective (cameras.cpp:433-456), 1 realistic (cameras.cpp:820-1019)
     float cameraFromRaster[16];  // row major
     float renderFromCamera[16];
     float lensRadius, focalDistance;
+    // realistic: lens elements {curvatureRadius, thickness, eta, apertureRadius} front to rear (metres),
+    // exit-pupil bounds {xmin, ymin, xmax, ymax} per film-radius bin, film extent and diagonal
+    const float *lens;
+    const float *pupilBounds;
+    int32_t nLens, nPupilBounds;
+    float physicalExtent[4];     // Bounds2f {pMin.x, pMin.y, pMax.x, pMax.y}
+    float filmDiagonal;
 };
 
 struct FilmDev {

@@ -58,9 +58,18 @@ class RenderScene:
         d = self.d
         r = capi.RenderDesc()
         r.camera_type = int(d["camera_type"][0])
-        r.camera_from_raster[:] = [float(x) for x in d["camera_from_raster"]]
         r.render_from_camera[:] = [float(x) for x in d["render_from_camera"]]
-        r.lens_radius, r.focal_distance = float(d["camera_params"][0]), float(d["camera_params"][1])
+        if r.camera_type == 1:  # RealisticCamera: lens table + exit-pupil bounds from the host
+            lens = np.ascontiguousarray(d["camera_lens"], np.float32).reshape(-1, 4)
+            pupil = np.ascontiguousarray(d["camera_exit_pupil"], np.float32).reshape(-1, 4)
+            r.n_lens_elements, r.lens_elements = len(lens), capi.fptr(lens)
+            r.n_exit_pupil_bounds, r.exit_pupil_bounds = len(pupil), capi.fptr(pupil)
+            r.physical_extent[:] = [float(x) for x in d["camera_extent"][:4]]
+            r.film_diagonal = float(d["camera_extent"][4])
+            keep += [lens, pupil]
+        else:
+            r.camera_from_raster[:] = [float(x) for x in d["camera_from_raster"]]
+            r.lens_radius, r.focal_distance = float(d["camera_params"][0]), float(d["camera_params"][1])
         r.film_type = int(d["film_type"][0]) if "film_type" in d else 0
         if r.film_type == 1:  # SpectralFilm
             r.n_buckets = int(d["film_spectral"][0])

@@ -463,6 +463,86 @@ def config3_pbrt(path, n_objects=32, grid=32, n_instances=4883, n_lights=1024, r
         f.write("\n".join(lines) + "\n")
 
 
+# A double-Gauss 50 mm f/2 prescription in pbrt's lens-file units (mm): curvature radius, thickness, index,
+# aperture diameter, front element first; radius 0 = the aperture stop (RealisticCamera::Create,
+# cameras.cpp:1380-1392; constructor :781-802).
+DGAUSS_50MM = [
+    (29.475, 3.76, 1.67, 25.2), (84.83, 0.12, 1.0, 25.2), (19.275, 4.025, 1.67, 23.0),
+    (40.77, 3.275, 1.699, 23.0), (12.75, 5.705, 1.0, 18.0), (0.0, 4.5, 0.0, 17.1),
+    (-14.495, 1.18, 1.603, 17.0), (40.77, 6.065, 1.658, 20.0), (-20.385, 0.19, 1.0, 20.0),
+    (437.065, 3.22, 1.717, 20.0), (-39.73, 5.0, 1.0, 20.0),
+]
+
+
+def chart_spectra(n=24, seed=2404):
+    """n smooth reflectance spectra on 10 nm knots over 380..720 nm (a Macbeth-like chart: the last six are a
+    grey ramp, the rest sums of two sigmoids / a bump), values in [0.03, 0.92]."""
+    rng = np.random.default_rng(seed)
+    lam = np.arange(380.0, 721.0, 10.0)
+    out = []
+    for k in range(n):
+        if k >= n - 6:
+            v = np.full_like(lam, 0.9 * 0.55 ** (k - (n - 6)))
+        else:
+            c0, c1 = rng.uniform(420, 680, 2)
+            w0, w1 = rng.uniform(15, 60, 2)
+            a0, a1 = rng.uniform(-0.6, 0.6, 2)
+            v = 0.35 + a0 / (1 + np.exp(-(lam - c0) / w0)) + a1 * np.exp(-0.5 * ((lam - c1) / w1) ** 2)
+        out.append(np.clip(v, 0.03, 0.92))
+    return lam, np.array(out)
+
+
+def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0, nbuckets=31, aperture_mm=12.0,
+                 focus=1.9, film="spectral", crop=None):
+    """BASELINE configs[3]: the Cornell room with a 24-patch spectral reflectance chart on the back wall, seen
+    through a RealisticCamera (double-Gauss 50 mm lens file written next to the scene) onto a SpectralFilm
+    with `nbuckets` bands over 395..705 nm (the ISET 31-band setting)."""
+    sc = cornell_box()
+    lens = os.path.splitext(path)[0] + "_lens.dat"
+    with open(lens, "w") as f:
+        f.write("# double-Gauss 50 mm: radius thickness eta aperture-diameter (mm)\n")
+        for e in DGAUSS_50MM:
+            f.write(" ".join(repr(float(x)) for x in e) + "\n")
+    white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
+    colours = [white, white, white, red, green, None, white, white]
+    cropw = f' "float cropwindow" [{crop[0]} {crop[1]} {crop[2]} {crop[3]}]' if crop else ''
+    lines = [
+        'LookAt 0.5 0.5 -1.4  0.5 0.5 0.5  0 1 0',
+        f'Camera "realistic" "string lensfile" "{lens}" "float aperturediameter" {aperture_mm} '
+        f'"float focusdistance" {focus}',
+        f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
+        f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "power"',
+        'PixelFilter "box"',
+        (f'Film "spectral" "string filename" "{os.path.splitext(out)[0]}.exr" "integer nbuckets" {nbuckets} '
+         f'"integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false' if film == "spectral" else
+         f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} '
+         '"bool savefp16" false') + cropw,
+        'WorldBegin',
+    ]
+    for m, c in zip(sc.meshes, colours):
+        lines.append('AttributeBegin')
+        if c is None:
+            lines.append('  AreaLightSource "diffuse" "rgb L" [17 12 4]')
+            lines.append('  Material "diffuse" "rgb reflectance" [0 0 0]')
+        else:
+            lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
+        lines.append('  ' + _mesh_pbrt(m))
+        lines.append('AttributeEnd')
+    lam, spectra = chart_spectra()
+    # 6 x 4 patches just in front of the back wall (z = 1), facing the camera
+    x0, y0, size, gap, z = 0.14, 0.52, 0.105, 0.018, 0.995
+    for k, v in enumerate(spectra):
+        i, j = k % 6, k // 6
+        xa, ya = x0 + i * (size + gap), y0 + (3 - j) * (size + gap) * 0.9
+        xb, yb = xa + size, ya + size * 0.9
+        sp = " ".join(f"{l:g} {r:.5f}" for l, r in zip(lam, v))
+        lines += ['AttributeBegin', f'  Material "diffuse" "spectrum reflectance" [{sp}]',
+                  '  ' + _mesh_pbrt(_quad([xa, ya, z], [xa, yb, z], [xb, yb, z], [xb, ya, z])), 'AttributeEnd']
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return sc
+
+
 def load_b2rs(path):
     """Reads the named-array container written by a host adaptor (oracle/dumpscene_ref.cpp is the
     test-side one): 'B2RS', u32 count, {u32 nameLen, name, u32 dtype, u32 ndim, u32 dims[], data}."""

@@ -85,6 +85,23 @@ TABLE_CASES = {
 # reference images (noise-gated: the scene has smooth glass, see NOISE_GATED)
 CONFIG3_FULL = dict(n_objects=32, grid=32, n_instances=4883, n_lights=1024, res=(1920, 1080), spp=1024, maxdepth=5)
 CONFIG3_SMALL = dict(n_objects=8, grid=12, n_instances=300, n_lights=96, res=(96, 54), spp=16, maxdepth=5)
+# BASELINE.json configs[3] (scenes.config4_pbrt): RealisticCamera + 31-band SpectralFilm.  Full size as tables
+# only (bench.py renders a bounded reference sample on the spot); in miniature with the reference's image.
+CONFIG4_FULL = dict(res=1024, spp=256, maxdepth=5)
+CONFIG4_SMALL = dict(res=64, spp=16, maxdepth=5)
+
+
+def make_config4_goldens(P, refrun, out):
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt = os.path.join(tmp, "c4.pbrt")
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), **CONFIG4_FULL)
+        refrun.dump_scene(pbrt, os.path.join(out, "config4_full.b2rs"))
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), **CONFIG4_SMALL)
+        refrun.dump_scene(pbrt, os.path.join(out, "config4_small.b2rs"))
+        img, names, secs = refrun.render_channels(pbrt)
+        np.save(os.path.join(out, "config4_small_ref.npy"), img.astype(np.float32))
+        print("config4_small", img.shape, names[:4], "mean", img[..., :3].mean(axis=(0, 1)), f"{secs:.2f}s")
 
 
 def make_render_goldens(P, refrun, out):
@@ -128,7 +145,11 @@ if __name__ == "__main__":
     import pbrt_v4_b200 as P
     import refrun
     out = os.path.dirname(os.path.abspath(__file__))
+    if "--config4-only" in sys.argv:
+        make_config4_goldens(P, refrun, out)
+        sys.exit(0)
     make_render_goldens(P, refrun, out)
+    make_config4_goldens(P, refrun, out)
     if "--render-only" in sys.argv:
         sys.exit(0)
     for name, (sc, rays) in cases(P.scenes).items():

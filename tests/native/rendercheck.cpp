@@ -74,6 +74,8 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.infiniteLights = rh.infiniteLights.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
+    rs.camera.lens = rh.lens.data();
+    rs.camera.pupilBounds = rh.pupilBounds.data();
     const int W = rh.width, H = rh.height;
     if (nThreads < 1) nThreads = 1;
     std::vector<std::thread> pool;
@@ -96,13 +98,14 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
                                 for (int i = 0; i < kNLambda; ++i) io.L[i] += io.Ld[i];
                         }
                         float out[4];
-                        FinishPath(rs, p.lambdaU, p.flags, p.filterWeight, [&](int i) { return io.L[i]; }, out);
+                        const float cw = p.cameraWeight;
+                        FinishPath(rs, p.lambdaU, p.flags, p.filterWeight, [&](int i) { return cw * io.L[i]; }, out);
                         double *px = rgbw + 4 * (size_t(y) * W + x);
                         for (int c = 0; c < 4; ++c) px[c] += out[c];
                         if (rs.film.type == 1) {  // spectral film: planes behind the rgbw block, as on the device
                             size_t nPix = size_t(W) * H, pix = size_t(y) * W + x;
                             double *bs = rgbw + 4 * nPix + pix, *ws = bs + size_t(rs.film.nBuckets) * nPix;
-                            SpectralFilmAdd(rs.film, p.lambdaU, p.filterWeight, [&](int i) { return io.L[i]; },
+                            SpectralFilmAdd(rs.film, p.lambdaU, p.filterWeight, [&](int i) { return cw * io.L[i]; },
                                             [&](int b, float v, float wt) {
                                                 bs[size_t(b) * nPix] += v;
                                                 ws[size_t(b) * nPix] += wt;
@@ -133,6 +136,8 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.infiniteLights = rh.infiniteLights.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
+    rs.camera.lens = rh.lens.data();
+    rs.camera.pupilBounds = rh.pupilBounds.data();
     int full = rs.integrator.maxDepth;
     for (int d = 0; d <= full; ++d) {
         rs.integrator.maxDepth = d;

@@ -132,3 +132,29 @@ def test_golden_image_spectral_film(P, rendercheck):
     assert abs(spec.mean() - ref[..., 3:].mean()) <= TOL_MEAN * ref[..., 3:].mean()
     # every sample put each of its 31 wavelengths into some bucket with weight 1
     np.testing.assert_array_equal(wsum.sum(axis=0), 31.0 * rsc.spp)
+
+
+def test_golden_image_config4_realistic_camera(P, rendercheck):
+    """BASELINE configs[3] in miniature: RealisticCamera (cameras.cpp:820-1019: exit-pupil sampling, the lens
+    trace, the cos^4 weight; vignetted samples add L = 0 with weight 1) onto a 31-band SpectralFilm, chart
+    patches with spectral reflectances.  Path-for-path agreement with the reference's image."""
+    name = "config4_small"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    assert int(rsc.d["camera_type"][0]) == 1 and rsc.n_buckets == 31
+    rgbw, bsum, wsum = rendercheck(rsc, full=True)
+    img = P.render.film_to_image(rgbw, rsc.d["film_matrix"])
+    assert rrmse(img, ref[..., :3]) <= TOL_RRMSE
+    assert abs(img.mean() - ref[..., :3].mean()) <= TOL_MEAN * ref[..., :3].mean()
+    spec = np.where(wsum > 0, bsum / np.where(wsum > 0, wsum, 1), 0).astype(np.float32).transpose(1, 2, 0)
+    assert rrmse(spec, ref[..., 3:]) <= TOL_RRMSE
+    np.testing.assert_array_equal(rgbw[..., 3], float(rsc.spp))
+
+
+def test_realistic_camera_description_is_validated(P, rendercheck):
+    rsc = P.RenderScene.load(os.path.join(GOLD, "config4_small.b2rs"))
+    d = dict(rsc.d)
+    d["camera_lens"] = rsc.d["camera_lens"].copy()
+    d["camera_lens"][0, 2] = 0.0  # a curved element with eta 0
+    with pytest.raises(AssertionError, match="eta 0"):
+        rendercheck(P.RenderScene(d))

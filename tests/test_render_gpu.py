@@ -176,3 +176,24 @@ def test_spectral_image_needs_a_spectral_film(P, cornell):
             r.spectral_image()
     finally:
         r.close()
+
+
+def test_config4_realistic_camera_spectral(P, rendercheck):
+    """BASELINE configs[3] in miniature on the device: RealisticCamera rays + 31-band SpectralFilm against the
+    reference's Film::GetImage, and against the CPU loop over the same headers."""
+    name = "config4_small"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img, spec = r.image(), r.spectral_image()
+        rgbw, bsum, wsum = r.film_all()
+    finally:
+        r.close()
+    assert rrmse(img, ref[..., :3]) <= TOL_RRMSE
+    assert abs(img.mean() - ref[..., :3].mean()) <= TOL_MEAN * ref[..., :3].mean()
+    assert rrmse(spec, ref[..., 3:]) <= TOL_RRMSE
+    np.testing.assert_array_equal(rgbw[..., 3], float(rsc.spp))
+    cpu = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
+    assert rrmse(img, cpu) <= 1e-4
