@@ -206,6 +206,27 @@ typedef struct b200pt_mesh_attr {
     uint32_t flip_normal; /* reverseOrientation ^ transformSwapsHandedness (util/mesh.h:42) */
 } b200pt_mesh_attr;
 
+/* One participating medium with a Henyey-Greenstein phase function and no emission.
+ * type 0 = HomogeneousMedium (media.h:217-262): sigma_a / sigma_s spectra (already times the medium's scale,
+ * as its DenselySampledSpectrum members hold them: interp 0 tables).
+ * type 1 = GridMedium (media.h:265-345, media.cpp GridMedium ctor): density on an nx * ny * nz grid over
+ * `bounds` in medium space (SampledGrid<Float>, x fastest), the ray is taken to medium space with
+ * medium_from_render (= renderFromMedium's inverse as the host holds it), majorants = the host's MajorantGrid
+ * (media.h:105-133): mres[3] voxels of max density, x fastest. */
+enum { B200PT_MEDIUM_HOMOGENEOUS = 0, B200PT_MEDIUM_GRID = 1 };
+typedef struct b200pt_medium {
+    uint32_t type;
+    int32_t sigma_a, sigma_s; /* spectrum indices */
+    float g;
+    float bounds[6];
+    float medium_from_render[16];
+    float render_from_medium[16];
+    int32_t nx, ny, nz;
+    const float *density;
+    int32_t mres[3];
+    const float *majorants;
+} b200pt_medium;
+
 typedef struct b200pt_render_desc {
     /* camera: 0 = perspective (cameras.cpp:433-456), 1 = realistic (fields at the end of this struct) */
     uint32_t camera_type;
@@ -261,6 +282,17 @@ typedef struct b200pt_render_desc {
     const float *exit_pupil_bounds;
     float physical_extent[4];
     float film_diagonal;
+    /* integrator_type 1 = VolPathIntegrator (cpu/integrators.cpp:953-1405; wavefront/media.cpp:22-354): participating
+     * media.  media[] are the scene's media; mesh_media[2 * m + {0, 1}] = {inside, outside} medium of mesh m's
+     * MediumInterface (cpu/primitive.cpp:50-109, interaction.h GetMedium), -1 = vacuum; a mesh whose two entries
+     * are equal is no medium transition (the ray keeps its medium).  NULL = no mesh has an interface.
+     * camera_medium = the medium camera rays start in (CameraBase::medium), -1 = none.
+     * integrator_type 0 = PathIntegrator ignores all of this. */
+    uint32_t integrator_type;
+    uint32_t n_media;
+    const struct b200pt_medium *media;
+    const int32_t *mesh_media;
+    int32_t camera_medium;
 } b200pt_render_desc;
 
 typedef struct b200pt_render b200pt_render;

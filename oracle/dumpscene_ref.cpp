@@ -32,6 +32,7 @@
 #include <pbrt/lights.h>
 #include <pbrt/lightsamplers.h>
 #include <pbrt/materials.h>
+#include <pbrt/media.h>
 #include <pbrt/options.h>
 #include <pbrt/parser.h>
 #include <pbrt/samplers.h>
@@ -334,6 +335,21 @@ int main(int argc, char **argv) {
     bool regularize = integratorParams.GetOneBool("regularize", false);
     int lsId = ls == "uniform" ? 0 : (ls == "power" ? 1 : 2);
     w.i32("integrator", {3}, {maxDepth, regularize ? 1 : 0, lsId});
+    if (integratorName != "path" && integratorName != "volpath") die("only the path and volpath integrators are dumped");
+    const bool volpath = integratorName == "volpath";
+    w.u32("integrator_type", {1}, {volpath ? 1u : 0u});
+    // media in the order of the scene's name -> Medium map; index -1 = no medium
+    std::map<const void *, int> mediumId;
+    {
+        int k = 0;
+        for (auto &kv : media) mediumId[kv.second.ptr()] = k++;
+    }
+    auto mediumIndex = [&](Medium m) -> int {
+        if (!m) return -1;
+        auto it = mediumId.find(m.ptr());
+        if (it == mediumId.end()) die("a medium that is not in the scene's medium table");
+        return it->second;
+    };
 
     // ---- geometry: walk the top-level BVH's ordered primitives (triangles only)
     if (!accel.Is<BVHAggregate>()) die("top-level aggregate is not a BVH");
@@ -350,6 +366,7 @@ int main(int argc, char **argv) {
     std::vector<int32_t> lightMeshTri(lights.size() * 2, -1);
     std::vector<int32_t> meshObject(nMesh, -1);
     // one triangle primitive of the world or of an object definition -> its mesh / material / light records
+    std::map<int, std::pair<int, int>> meshMediaOf;  // reference mesh index -> {inside, outside}
     auto visitTriangle = [&](const Primitive &p, int object, std::vector<uint32_t> &primsOut) {
         Shape shape;
         pbrt::Material mtl;
@@ -362,13 +379,16 @@ int main(int argc, char **argv) {
             mtl = gp->material;
             area = gp->areaLight;
             if (gp->alpha) die("alpha textures are not dumped");
+            if (volpath && gp->mediumInterface.IsMediumTransition())
+                meshMediaOf[shape.Cast<Triangle>()->meshIndex] = {mediumIndex(gp->mediumInterface.inside),
+                                                                  mediumIndex(gp->mediumInterface.outside)};
         } else
             die("only triangle primitives are dumped so far");
         if (!shape.Is<Triangle>()) die("only triangles are dumped so far");
         const Triangle *t = shape.Cast<Triangle>();
         int m = t->meshIndex;
         primsOut.insert(primsOut.end(), {0u, uint32_t(m), uint32_t(t->triIndex)});
-        if (!materialId.count(mtl.ptr())) {
+        if (mtl && !materialId.count(mtl.ptr())) {
             materialId[mtl.ptr()] = int(materialList.size());
             materialList.push_back(mtl);
         }
@@ -476,6 +496,52 @@ int main(int argc, char **argv) {
     w.i32("indices", {uint32_t(idx.size() / 3), 3}, idx);
     w.i32("mesh_attr", {uint32_t(nMesh), 3}, meshAttr);
     w.i32("mesh_object", {uint32_t(nMesh)}, meshObject);
+    if (volpath) {
+        std::vector<int32_t> mm(nMesh * 2, -1);
+        for (auto &kv : meshMediaOf)
+            if (meshRemap[kv.first] >= 0) {
+                mm[2 * meshRemap[kv.first]] = kv.second.first;
+                mm[2 * meshRemap[kv.first] + 1] = kv.second.second;
+            }
+        w.i32("mesh_media", {uint32_t(nMesh), 2}, mm);
+        Medium camMedium = camera.Is<PerspectiveCamera>() ? camera.Cast<PerspectiveCamera>()->medium
+                                                          : camera.Cast<RealisticCamera>()->medium;
+        w.i32("camera_medium", {1}, {mediumIndex(camMedium)});
+        // media_i: {type, sigma_a, sigma_s, nx, ny, nz, mres[3]}; media_f: {g, bounds[6], mediumFromRender[16],
+        // renderFromMedium[16]} (include/b200pt.h b200pt_medium)
+        std::vector<int32_t> mi;
+        std::vector<float> mf;
+        int k = 0;
+        for (auto &kv : media) {
+            Medium m = kv.second;
+            if (m.IsEmissive()) die("emissive media are not dumped");
+            float rec[39] = {0};
+            if (const HomogeneousMedium *hm = m.CastOrNullptr<HomogeneousMedium>()) {
+                mi.insert(mi.end(), {0, pool.add(&hm->sigma_a_spec, 0), pool.add(&hm->sigma_s_spec, 0), 0, 0, 0, 0, 0, 0});
+                rec[0] = hm->phase.g;
+            } else if (const GridMedium *gm = m.CastOrNullptr<GridMedium>()) {
+                const SampledGrid<Float> &dg = gm->densityGrid;
+                const MajorantGrid &mg = gm->majorantGrid;
+                mi.insert(mi.end(), {1, pool.add(&gm->sigma_a_spec, 0), pool.add(&gm->sigma_s_spec, 0), dg.nx, dg.ny, dg.nz,
+                                     mg.res.x, mg.res.y, mg.res.z});
+                rec[0] = gm->phase.g;
+                const Bounds3f &b = gm->bounds;
+                float bb[6] = {b.pMin.x, b.pMin.y, b.pMin.z, b.pMax.x, b.pMax.y, b.pMax.z};
+                memcpy(rec + 1, bb, 24);
+                std::vector<float> a = Mat(gm->renderFromMedium.GetInverseMatrix()), c = Mat(gm->renderFromMedium.GetMatrix());
+                memcpy(rec + 7, a.data(), 64);
+                memcpy(rec + 23, c.data(), 64);
+                std::vector<float> dens(dg.values.begin(), dg.values.end()), maj(mg.voxels.begin(), mg.voxels.end());
+                w.f32("medium_density_" + std::to_string(k), {uint32_t(dg.nz), uint32_t(dg.ny), uint32_t(dg.nx)}, dens);
+                w.f32("medium_majorants_" + std::to_string(k), {uint32_t(mg.res.z), uint32_t(mg.res.y), uint32_t(mg.res.x)}, maj);
+            } else
+                die("only homogeneous and uniformgrid media are dumped so far");
+            mf.insert(mf.end(), rec, rec + 39);
+            ++k;
+        }
+        w.i32("media_i", {uint32_t(k), 9}, mi);
+        w.f32("media_f", {uint32_t(k), 39}, mf);
+    }
     if (!instObject.empty()) {
         w.i32("instance_object", {uint32_t(instObject.size())}, instObject);
         w.f32("instance_m", {uint32_t(instObject.size()), 16}, instM);

@@ -138,6 +138,13 @@ class MeshAttr(C.Structure):
     _fields_ = [("material", C.c_int32), ("light_first", C.c_int32), ("flip_normal", C.c_uint32)]
 
 
+class Medium(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("sigma_a", C.c_int32), ("sigma_s", C.c_int32), ("g", C.c_float),
+                ("bounds", C.c_float * 6), ("medium_from_render", C.c_float * 16),
+                ("render_from_medium", C.c_float * 16), ("nx", C.c_int32), ("ny", C.c_int32), ("nz", C.c_int32),
+                ("density", C.POINTER(C.c_float)), ("mres", C.c_int32 * 3), ("majorants", C.POINTER(C.c_float))]
+
+
 class RenderDesc(C.Structure):
     _fields_ = [("camera_type", C.c_uint32), ("camera_from_raster", C.c_float * 16),
                 ("render_from_camera", C.c_float * 16), ("lens_radius", C.c_float), ("focal_distance", C.c_float),
@@ -154,7 +161,9 @@ class RenderDesc(C.Structure):
                 ("n_buckets", C.c_uint32), ("lambda_min", C.c_float), ("lambda_max", C.c_float),
                 ("n_lens_elements", C.c_uint32), ("lens_elements", C.POINTER(C.c_float)),
                 ("n_exit_pupil_bounds", C.c_uint32), ("exit_pupil_bounds", C.POINTER(C.c_float)),
-                ("physical_extent", C.c_float * 4), ("film_diagonal", C.c_float)]
+                ("physical_extent", C.c_float * 4), ("film_diagonal", C.c_float),
+                ("integrator_type", C.c_uint32), ("n_media", C.c_uint32), ("media", C.POINTER(Medium)),
+                ("mesh_media", C.POINTER(C.c_int32)), ("camera_medium", C.c_int32)]
 
 
 class RenderStats(C.Structure):

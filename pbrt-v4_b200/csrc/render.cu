@@ -20,8 +20,11 @@ constexpr int kShadeBlock = 128;
 
 static size_t Al(size_t b) { return (b + 255) & ~size_t(255); }
 
-size_t PassBufferBytes(long long n, int depthSlots) {
+size_t PassBufferBytes(long long n, int depthSlots, bool vol) {
     size_t t = 0;
+    if (vol)
+        t += 5 * Al(sizeof(float) * kNLambda * n) + Al(sizeof(uint32_t) * kShadowAuxWords * n) +
+             Al(sizeof(uint32_t) * 6 * n) + Al(sizeof(int));
     t += 2 * Al(sizeof(float) * kNLambda * n);         // beta, L
     t += Al(sizeof(float) * kPathScalars * n);
     t += Al(sizeof(int) * kPathInts * n);
@@ -34,7 +37,7 @@ size_t PassBufferBytes(long long n, int depthSlots) {
     return t;
 }
 
-void CarvePassBuffers(void *base, long long n, int depthSlots, PassBuffers &pb) {
+void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuffers &pb) {
     char *p = static_cast<char *>(base);
     auto take = [&](size_t b) {
         char *r = p;
@@ -57,6 +60,19 @@ void CarvePassBuffers(void *base, long long n, int depthSlots, PassBuffers &pb) 
     pb.occluded = (unsigned char *)take(size_t(n));
     pb.counts = (int *)take(sizeof(int) * kCountStride * depthSlots);
     pb.maxDepthSlots = depthSlots;
+    pb.ru = pb.rl = pb.shT = pb.shRl = pb.shRu = nullptr;
+    pb.shAux = pb.shHits = nullptr;
+    pb.shContinue = nullptr;
+    if (vol) {
+        pb.ru = (float *)take(sizeof(float) * kNLambda * n);
+        pb.rl = (float *)take(sizeof(float) * kNLambda * n);
+        pb.shT = (float *)take(sizeof(float) * kNLambda * n);
+        pb.shRl = (float *)take(sizeof(float) * kNLambda * n);
+        pb.shRu = (float *)take(sizeof(float) * kNLambda * n);
+        pb.shAux = (uint32_t *)take(sizeof(uint32_t) * kShadowAuxWords * n);
+        pb.shHits = (uint32_t *)take(sizeof(uint32_t) * 6 * n);
+        pb.shContinue = (int *)take(sizeof(int));
+    }
 }
 
 // ---- queue push: one atomic per group of converged lanes
@@ -91,6 +107,7 @@ __device__ __forceinline__ void StoreHeader(const PassBuffers &pb, int i, const 
     q[1 * n] = p.dimension;
     q[2 * n] = p.depth;
     q[3 * n] = (int)p.flags;
+    q[4 * n] = p.medium;
 }
 
 __device__ __forceinline__ void LoadHeader(const PassBuffers &pb, int i, PathRegs &p) {
@@ -108,6 +125,7 @@ __device__ __forceinline__ void LoadHeader(const PassBuffers &pb, int i, PathReg
     p.dimension = q[1 * n];
     p.depth = q[2 * n];
     p.flags = (uint32_t)q[3 * n];
+    p.medium = q[4 * n];
     p.filterWeight = 1.f;
 }
 
@@ -130,6 +148,46 @@ struct DevIO {
         StoreRay(pb.shRays, slot, o, d, valid ? tMax : -1.f);
         pb.shPath[slot] = valid ? path : -1;
     }
+    // volpath: r_u / r_l live in global memory ([k][path]); a light sample also records what its walk needs
+    __device__ __forceinline__ float Ru(int k) const { return pb.ru[(long long)k * pb.n + path]; }
+    __device__ __forceinline__ void SetRu(int k, float v) { pb.ru[(long long)k * pb.n + path] = v; }
+    __device__ __forceinline__ float Rl(int k) const { return pb.rl[(long long)k * pb.n + path]; }
+    __device__ __forceinline__ void SetRl(int k, float v) { pb.rl[(long long)k * pb.n + path] = v; }
+    __device__ void ShadowEndVol(bool valid, V3 o, V3 d, float tMax, const ShadowVolInfo &info) {
+        ShadowEnd(valid, o, d, tMax);
+        if (!valid) return;
+        uint32_t *a = pb.shAux + (long long)kShadowAuxWords * slot;
+        a[0] = __float_as_uint(info.p_l);
+        a[1] = __float_as_uint(info.scatterPDF);
+        a[2] = (uint32_t)info.medium;
+        a[3] = 0;  // the walk has not started: T_ray = r_l = r_u = 1, rng seeded from the ray
+        const float lp[9] = {info.lightPi.lo.x, info.lightPi.lo.y, info.lightPi.lo.z, info.lightPi.hi.x, info.lightPi.hi.y,
+                             info.lightPi.hi.z, info.lightN.x, info.lightN.y, info.lightN.z};
+        for (int i = 0; i < 9; ++i) a[8 + i] = __float_as_uint(lp[i]);
+    }
+};
+
+// IO of the medium kernel and of escaped rays: everything in global memory, indexed by path
+struct GlobalIO {
+    const PassBuffers &pb;
+    int path;
+    int *nShadow;
+    int slot;
+    __device__ GlobalIO(const PassBuffers &b, int pathId, int *shadowCount) : pb(b), path(pathId), nShadow(shadowCount), slot(-1) {}
+    __device__ __forceinline__ float Beta(int k) const { return pb.beta[(long long)k * pb.n + path]; }
+    __device__ __forceinline__ void SetBeta(int k, float v) { pb.beta[(long long)k * pb.n + path] = v; }
+    __device__ __forceinline__ float Ru(int k) const { return pb.ru[(long long)k * pb.n + path]; }
+    __device__ __forceinline__ void SetRu(int k, float v) { pb.ru[(long long)k * pb.n + path] = v; }
+    __device__ __forceinline__ float Rl(int k) const { return pb.rl[(long long)k * pb.n + path]; }
+    __device__ __forceinline__ void SetRl(int k, float v) { pb.rl[(long long)k * pb.n + path] = v; }
+    __device__ __forceinline__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
+    __device__ __forceinline__ void ShadowBegin() { slot = QueuePush(nShadow); }
+    __device__ __forceinline__ void SetLd(int k, float v) { pb.Ld[(long long)k * pb.n + slot] = v; }
+    __device__ void ShadowEndVol(bool valid, V3 o, V3 d, float tMax, const ShadowVolInfo &info) {
+        DevIO tmp(pb, path, nShadow, nullptr);
+        tmp.slot = slot;
+        tmp.ShadowEndVol(valid, o, d, tMax, info);
+    }
 };
 
 // ---- camera rays: RayIntegrator::EvaluatePixelSample up to GenerateRay (cpu/integrators.cpp:228-262)
@@ -148,6 +206,13 @@ GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nA
         pb.beta[k * n + i] = 1.f;
         pb.L[k * n + i] = 0.f;
     }
+    if (pb.ru) {
+#pragma unroll
+        for (int k = 0; k < kNLambda; ++k) {
+            pb.ru[k * n + i] = 1.f;
+            pb.rl[k * n + i] = 1.f;
+        }
+    }
     StoreHeader(pb, i, p);
     pb.scalars[kCameraWeightScalar * n + i] = p.cameraWeight;
     // a sample without a camera ray (vignetted by the lens system) keeps its queue slot with a ray that
@@ -163,8 +228,12 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
     int *counts = pb.counts + kCountStride * depth;
     if (t >= counts[0]) return;
     uint32_t slot = pb.hits[6ll * t];
+    if (slot == kConsumedTag) return;  // absorbed or scattered in a medium (VolMediumKernel)
     if (slot == kMissTag) {  // escaped: infinite lights add their radiance, the path ends
-        if (rs.nInfiniteLights && pb.rays[depth & 1][7ll * t + 6] >= 0) {
+        if (rs.nInfiniteLights && rs.integrator.type == 1 && pb.rays[depth & 1][7ll * t + 6] >= 0) {
+            GlobalIO io(pb, pb.rayPath[depth & 1][t], nullptr);
+            EscapedRadianceVol(rs, pb.scalars[io.path], io);
+        } else if (rs.nInfiniteLights && pb.rays[depth & 1][7ll * t + 6] >= 0) {
             struct {
                 const PassBuffers &pb;
                 int path;
@@ -190,7 +259,7 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
 #define B2_SHADE_MIN_BLOCKS 4  // 128 registers: the layered walks are latency bound, four blocks per SM beat three
 #endif
 // ---- one path vertex: PathIntegrator::Li loop body (cpu/integrators.cpp:640-760)
-template <int MAT, int LBVH>
+template <int MAT, int LBVH, int VOL>
 __global__ void __launch_bounds__(kShadeBlock, B2_SHADE_MIN_BLOCKS)
 ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -219,7 +288,7 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     uint2 h0 = h[0], h1 = h[1], h2 = h[2];
     hit[0] = h0.x; hit[1] = h0.y; hit[2] = h1.x; hit[3] = h1.y; hit[4] = h2.x; hit[5] = h2.y;
     DevIO io(pb, path, counts + 1, myBeta);
-    ShadeVertex<DevIO, MAT, LBVH>(rs, p, hit, io);
+    ShadeVertex<DevIO, MAT, LBVH, VOL>(rs, p, hit, io);
     if (p.flags & PF_ALIVE) {
         int *next = pb.counts + kCountStride * (depth + 1);
         int slot = QueuePush(next);
@@ -231,6 +300,106 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     } else {
         pb.ints[3 * n + path] = (int)p.flags;  // the finish kernel needs PF_TERMINATED_SECONDARY
     }
+}
+
+// ---- volpath: the rays of this iteration that travel in a medium (cpu/integrators.cpp:968-1075).  Absorbed and
+// scattered paths are finished here (their hit slot is marked consumed); survivors go on to classify / shade
+// with beta, r_u, r_l rescaled.
+template <int LBVH>
+__global__ void __launch_bounds__(kShadeBlock)
+VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int *counts = pb.counts + kCountStride * depth;
+    if (t >= counts[0]) return;
+    const int cur = depth & 1, nxt = cur ^ 1;
+    const long long n = pb.n;
+    int path = pb.rayPath[cur][t];
+    if (pb.ints[4 * n + path] < 0) return;  // not in a medium
+    const float *r = pb.rays[cur] + 7ll * t;
+    if (r[6] < 0) return;  // a sample without a camera ray
+    PathRegs p;
+    LoadHeader(pb, path, p);
+    int pix = path % nPixels;
+    p.px = rs.film.x0 + pix % width;
+    p.py = rs.film.y0 + pix / width;
+    p.rayO = mk(r[0], r[1], r[2]);
+    p.rayD = mk(r[3], r[4], r[5]);
+    p.rayTMax = r[6];
+    uint32_t slot = pb.hits[6ll * t];
+    float tHit = slot == kMissTag ? INFINITY : __uint_as_float(pb.hits[6ll * t + 1]);
+    GlobalIO io(pb, path, counts + 1);
+    int res = VolMediumStep<GlobalIO, LBVH>(rs, p, tHit, io);
+    if (res == VOL_SURVIVE) {
+        StoreHeader(pb, path, p);
+        return;
+    }
+    pb.hits[6ll * t] = kConsumedTag;
+    if (res == VOL_TERMINATED) {
+        pb.ints[3 * n + path] = (int)(p.flags & ~PF_ALIVE);
+        return;
+    }
+    int *next = pb.counts + kCountStride * (depth + 1);
+    int ns = QueuePush(next);
+    StoreRay(pb.rays[nxt], ns, p.rayO, p.rayD, p.rayTMax);
+    pb.rayPath[nxt][ns] = path;
+    StoreHeader(pb, path, p);
+}
+
+// ---- volpath: one segment of every light sample's transmittance walk (cpu/integrators.cpp:1334-1395).  pb.shHits
+// holds the closest hits of the shadow rays.  A walk that reaches the light adds its estimate to the path's
+// radiance; one that meets an interface leaves its next ray in the same slot and counts in pb.shContinue.
+__global__ void __launch_bounds__(kShadeBlock)
+ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= pb.counts[kCountStride * depth + 1]) return;
+    int path = pb.shPath[t];
+    if (path < 0) return;
+    const long long n = pb.n;
+    float *ray = pb.shRays + 7ll * t;
+    uint32_t *a = pb.shAux + (long long)kShadowAuxWords * t;
+    ShadowRegs sh;
+    sh.o = mk(ray[0], ray[1], ray[2]);
+    sh.d = mk(ray[3], ray[4], ray[5]);
+    sh.medium = (int)a[2];
+    sh.lightPi.lo = mk(__uint_as_float(a[8]), __uint_as_float(a[9]), __uint_as_float(a[10]));
+    sh.lightPi.hi = mk(__uint_as_float(a[11]), __uint_as_float(a[12]), __uint_as_float(a[13]));
+    sh.lightN = mk(__uint_as_float(a[14]), __uint_as_float(a[15]), __uint_as_float(a[16]));
+    float T[kNLambda], rl[kNLambda], ru[kNLambda];
+    const bool started = a[3] != 0;
+    if (started) {
+        sh.rng.state = (uint64_t)a[4] | ((uint64_t)a[5] << 32);
+        sh.rng.inc = (uint64_t)a[6] | ((uint64_t)a[7] << 32);
+        for (int k = 0; k < kNLambda; ++k) {
+            T[k] = pb.shT[k * n + t];
+            rl[k] = pb.shRl[k * n + t];
+            ru[k] = pb.shRu[k * n + t];
+        }
+    } else {
+        sh.rng = PcgSeed(Hash3f(sh.o.x, sh.o.y, sh.o.z), Hash3f(sh.d.x, sh.d.y, sh.d.z));
+        for (int k = 0; k < kNLambda; ++k) T[k] = rl[k] = ru[k] = 1.f;
+    }
+    uint32_t hit[6];
+    for (int i = 0; i < 6; ++i) hit[i] = pb.shHits[6ll * t + i];
+    int res = ShadowTrSegment(rs, pb.scalars[path], sh, hit, T, rl, ru);
+    if (res == SHADOW_CONTINUE) {
+        StoreRay(pb.shRays, t, sh.o, sh.d, ray[6]);
+        a[2] = (uint32_t)sh.medium;
+        a[3] = 1;
+        a[4] = (uint32_t)sh.rng.state; a[5] = (uint32_t)(sh.rng.state >> 32);
+        a[6] = (uint32_t)sh.rng.inc;   a[7] = (uint32_t)(sh.rng.inc >> 32);
+        for (int k = 0; k < kNLambda; ++k) {
+            pb.shT[k * n + t] = T[k];
+            pb.shRl[k * n + t] = rl[k];
+            pb.shRu[k * n + t] = ru[k];
+        }
+        atomicAdd(pb.shContinue, 1);
+        return;
+    }
+    if (res == SHADOW_REACHED)
+        ShadowTrFinish(T, rl, ru, __uint_as_float(a[0]), __uint_as_float(a[1]), [&](int k) { return pb.Ld[k * n + t]; },
+                       [&](int k) { return pb.ru[k * n + path]; }, [&](int k, float v) { pb.L[k * n + path] += v; });
+    pb.shPath[t] = -1;
+    ray[6] = -1.f;
 }
 
 // ---- unoccluded light samples join the path's radiance (RecordShadowRayResult, wavefront/intersect.h:176-190)
@@ -350,13 +519,17 @@ cudaError_t LaunchClassify(const RenderSceneDev &rs, const PassBuffers &pb, int 
 cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width,
                         int nActive, uint32_t matMask, cudaStream_t stream, int *launches) {
     int grid = Blocks(nActive, kShadeBlock);
-    const bool lbvh = rs.integrator.lightSampler == 2;
+    const bool lbvh = rs.integrator.lightSampler == 2, vol = rs.integrator.type == 1;
 #define B2_SHADE(bit, MAT)                                                                              \
     if (matMask & (bit)) {                                                                              \
-        if (lbvh)                                                                                       \
-            ShadeKernel<MAT, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);       \
+        if (vol && lbvh)                                                                                \
+            ShadeKernel<MAT, 1, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
+        else if (vol)                                                                                   \
+            ShadeKernel<MAT, 0, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
+        else if (lbvh)                                                                                  \
+            ShadeKernel<MAT, 1, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
         else                                                                                            \
-            ShadeKernel<MAT, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);       \
+            ShadeKernel<MAT, 0, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
         ++*launches;                                                                                    \
     }
     B2_SHADE(1u, MAT_DIFFUSE)
@@ -364,6 +537,19 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
     B2_SHADE(4u, MAT_DIELECTRIC)
     B2_SHADE(8u, MAT_COATED_DIFFUSE)
 #undef B2_SHADE
+    return cudaGetLastError();
+}
+cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width, int nActive,
+                            cudaStream_t stream) {
+    int grid = Blocks(nActive, kShadeBlock);
+    if (rs.integrator.lightSampler == 2)
+        VolMediumKernel<1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
+    else
+        VolMediumKernel<0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
+    return cudaGetLastError();
+}
+cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {
+    ShadowTrKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth);
     return cudaGetLastError();
 }
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {

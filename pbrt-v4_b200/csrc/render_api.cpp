@@ -24,6 +24,8 @@ struct b200pt_render {
     void *dSpectra = nullptr, *dMaterials = nullptr, *dLights = nullptr, *dMeshes = nullptr;
     void *dLightBvh = nullptr, *dBitTrails = nullptr, *dInfinite = nullptr;
     void *dLens = nullptr, *dPupil = nullptr;
+    void *dMedia = nullptr;
+    std::vector<void *> dGrids;  // density and majorant grids of the media
     double *dFilm = nullptr;
     float *dImage = nullptr;
     void *dPaths = nullptr;
@@ -66,6 +68,8 @@ int b200pt_render_destroy(b200pt_render *r) {
     cudaFree(r->dBitTrails);
     cudaFree(r->dInfinite);
     cudaFree(r->dLens);
+    cudaFree(r->dMedia);
+    for (void *g : r->dGrids) cudaFree(g);
     cudaFree(r->dPupil);
     cudaFree(r->dFilm);
     cudaFree(r->dImage);
@@ -104,8 +108,20 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         (rc = Upload(ctx, r->host.infiniteLights, &r->dInfinite)) || (rc = Upload(ctx, r->host.lens, &r->dLens)) ||
         (rc = Upload(ctx, r->host.pupilBounds, &r->dPupil)))
         return fail(rc);
+    for (size_t i = 0; i < r->host.media.size(); ++i) {  // grids first: the medium table points at them
+        if (r->host.media[i].type != 1) continue;
+        void *dd = nullptr, *dm = nullptr;
+        if ((rc = Upload(ctx, r->host.mediumGrids[i].first, &dd))) return fail(rc);
+        r->dGrids.push_back(dd);
+        if ((rc = Upload(ctx, r->host.mediumGrids[i].second, &dm))) return fail(rc);
+        r->dGrids.push_back(dm);
+        r->host.media[i].density = (const float *)dd;
+        r->host.media[i].majorants = (const float *)dm;
+    }
+    if ((rc = Upload(ctx, r->host.media, &r->dMedia))) return fail(rc);
     r->nPixels = r->host.width * r->host.height;
     r->dev = r->host.rs;
+    r->dev.media = (const MediumDev *)r->dMedia;
     r->dev.spectra = (const SpectrumTable *)r->dSpectra;
     r->dev.materials = (const MaterialDev *)r->dMaterials;
     r->dev.lights = (const LightDev *)r->dLights;
@@ -164,18 +180,19 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
     const DeviceScene &sc = r->scene->dev;
     const int stackDepth = int(sc.maxDepth) + 1;
     const int maxDepth = r->dev.integrator.maxDepth;
-    const int depthSlots = maxDepth + 2;
+    const bool vol = r->dev.integrator.type == 1;
+    const int depthSlots = vol ? kVolMaxIterations + 2 : maxDepth + 2;
     if (need > r->pathCap) {
         B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         cudaFree(r->dPaths);
         r->dPaths = nullptr;
         r->pathCap = 0;
-        if (cudaMalloc(&r->dPaths, PassBufferBytes(need, depthSlots)) != cudaSuccess) {
+        if (cudaMalloc(&r->dPaths, PassBufferBytes(need, depthSlots, vol)) != cudaSuccess) {
             (void)cudaGetLastError();
             ctx->err = "render_run: out of device memory for the path buffers";
             return B200PT_ERR_NOMEM;
         }
-        CarvePassBuffers(r->dPaths, need, depthSlots, r->pb);
+        CarvePassBuffers(r->dPaths, need, depthSlots, vol, r->pb);
         r->pathCap = need;
     }
     const PassBuffers &pb = r->pb;
@@ -189,6 +206,53 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
         B2_CUDA(ctx, LaunchGenerate(r->dev, pb, nPix, width, nActive, first_sample + done * sample_stride,
                                     sample_stride, ctx->stream));
         ++launches;
+        if (vol) {
+            // VolPathIntegrator: iteration j = one pass of Li's while loop for every live path (a medium event, a
+            // surface vertex or an interface crossing), until no ray is left.  Queue lengths are read back once per
+            // iteration (interface crossings do not count as depth, so the iteration count is not known ahead).
+            int usedIters = 0;
+            for (int j = 0; j < kVolMaxIterations; ++j) {
+                const int *nRays = pb.counts + kCountStride * j, *nShadow = nRays + 1;
+                B2_CUDA(ctx, LaunchTraversePersist(sc, pb.rays[j & 1], nActive, (b200pt_hit *)pb.hits, nullptr, false,
+                                                   r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
+                                                   ctx->nodeMin, ctx->stream, true, nRays));
+                ++launches;
+                if (r->dev.nMedia) {
+                    B2_CUDA(ctx, LaunchVolMedium(r->dev, pb, j, nPix, width, nActive, ctx->stream));
+                    ++launches;
+                }
+                B2_CUDA(ctx, LaunchClassify(r->dev, pb, j, nActive, ctx->stream));
+                ++launches;
+                B2_CUDA(ctx, LaunchShade(r->dev, pb, j, nPix, width, nActive, r->matMask, ctx->stream, &launches));
+                int hc[2] = {0, 0};  // light samples of this iteration, rays of the next
+                B2_CUDA(ctx, cudaMemcpyAsync(&hc[0], nShadow, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+                B2_CUDA(ctx, cudaMemcpyAsync(&hc[1], pb.counts + kCountStride * (j + 1), sizeof(int), cudaMemcpyDeviceToHost,
+                                             ctx->stream));
+                B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                usedIters = j + 1;
+                // the transmittance walks: closest hit of every light-sample ray, one segment, until none goes on
+                for (int live = hc[0], seg = 0; live > 0 && seg < 64; ++seg) {
+                    B2_CUDA(ctx, cudaMemsetAsync(pb.shContinue, 0, sizeof(int), ctx->stream));
+                    B2_CUDA(ctx, LaunchTraversePersist(sc, pb.shRays, hc[0], (b200pt_hit *)pb.shHits, nullptr, false,
+                                                       r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
+                                                       ctx->nodeMin, ctx->stream, true, nShadow));
+                    B2_CUDA(ctx, LaunchShadowTr(r->dev, pb, j, hc[0], ctx->stream));
+                    launches += 2;
+                    B2_CUDA(ctx, cudaMemcpyAsync(&live, pb.shContinue, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+                    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                }
+                if (hc[1] == 0) break;
+            }
+            B2_CUDA(ctx, LaunchFinish(r->dev, pb, nActive, ctx->stream));
+            B2_CUDA(ctx, LaunchFilmAdd(pb, nPix, ns, r->dFilm, ctx->stream));
+            if (r->dev.film.type == 1) {
+                B2_CUDA(ctx, LaunchFilmAddSpectral(r->dev.film, pb, nPix, ns, r->dFilm, ctx->stream));
+                ++launches;
+            }
+            B2_CUDA(ctx, LaunchSumCounts(pb, usedIters, r->dCounters, ctx->stream));
+            launches += 3;
+            continue;
+        }
         // vertex j: closest hit of the rays in queue j -> material queues -> shading (next rays into queue
         // j+1, light samples into the shadow queue) -> visibility of the light samples -> radiance.
         // Vertex maxDepth only collects emission (cpu/integrators.cpp:690-692).

@@ -98,6 +98,42 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     rs.integrator.maxDepth = d->max_depth;
     rs.integrator.regularize = d->regularize;
     rs.integrator.lightSampler = d->light_sampler;
+    rs.integrator.type = d->integrator_type;
+    if (d->integrator_type > 1) return bad("unsupported integrator type (0 path, 1 volpath)");
+    rs.camera.medium = -1;
+    rs.nMedia = 0;
+    rs.media = nullptr;
+    if (d->integrator_type == 1) {
+        if (d->n_media && !d->media) return bad("null media table");
+        if (d->camera_medium < -1 || d->camera_medium >= int32_t(d->n_media)) return bad("camera medium out of range");
+        rs.camera.medium = d->camera_medium;
+        rs.nMedia = d->n_media;
+        out.media.resize(d->n_media);
+        out.mediumGrids.resize(d->n_media);
+        for (uint32_t i = 0; i < d->n_media; ++i) {
+            const b200pt_medium &m = d->media[i];
+            if (m.type > B200PT_MEDIUM_GRID) return bad("unsupported medium type");
+            if (!specOk(m.sigma_a) || !specOk(m.sigma_s)) return bad("medium spectrum index out of range");
+            MediumDev &o = out.media[i];
+            std::memset(&o, 0, sizeof o);
+            o.type = m.type;
+            o.sigmaA = m.sigma_a;
+            o.sigmaS = m.sigma_s;
+            o.g = m.g;
+            if (m.type == B200PT_MEDIUM_GRID) {
+                if (m.nx < 1 || m.ny < 1 || m.nz < 1 || !m.density) return bad("grid medium without a density grid");
+                if (m.mres[0] < 1 || m.mres[1] < 1 || m.mres[2] < 1 || !m.majorants)
+                    return bad("grid medium without a majorant grid");
+                std::memcpy(o.bounds, m.bounds, 24);
+                std::memcpy(o.mediumFromRender, m.medium_from_render, 64);
+                std::memcpy(o.renderFromMedium, m.render_from_medium, 64);
+                o.nx = m.nx; o.ny = m.ny; o.nz = m.nz;
+                for (int c = 0; c < 3; ++c) o.mres[c] = m.mres[c];
+                out.mediumGrids[i].first.assign(m.density, m.density + size_t(m.nx) * m.ny * m.nz);
+                out.mediumGrids[i].second.assign(m.majorants, m.majorants + size_t(m.mres[0]) * m.mres[1] * m.mres[2]);
+            }
+        }
+    }
 
     out.spectra.resize(d->n_spectra);
     for (uint32_t i = 0; i < d->n_spectra; ++i) {
@@ -146,7 +182,14 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         const b200pt_mesh_attr &m = d->meshes[i];
         if (m.material >= int32_t(d->n_materials)) return bad("mesh material index out of range");
         if (m.light_first >= int32_t(d->n_lights)) return bad("mesh light index out of range");
-        out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, 0};
+        int32_t mi = -1, mo = -1;
+        if (d->integrator_type == 1 && d->mesh_media) {
+            mi = d->mesh_media[2 * i];
+            mo = d->mesh_media[2 * i + 1];
+            if (mi < -1 || mo < -1 || mi >= int32_t(d->n_media) || mo >= int32_t(d->n_media))
+                return bad("mesh medium index out of range");
+        }
+        out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, 0, mi, mo};
     }
     out.lights.resize(d->n_lights);
     for (uint32_t i = 0; i < d->n_lights; ++i) {

@@ -2,6 +2,7 @@
 // uploads them, tests/native/rendercheck.cpp uses them in place).  Pure host code.
 #pragma once
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/b200pt.h"
@@ -19,6 +20,8 @@ struct RenderHost {
     std::vector<uint32_t> lightBvhNodes;   // 8 per node
     std::vector<uint32_t> lightBitTrails;  // per light
     std::vector<int32_t> infiniteLights;   // light indices
+    std::vector<MediumDev> media;          // density / majorants pointers are filled by the owner of the grids
+    std::vector<std::pair<std::vector<float>, std::vector<float>>> mediumGrids;  // per medium: density, majorants
     std::vector<float> lens, pupilBounds;  // realistic camera: 4 floats per element / per film-radius bin
     int width = 0, height = 0;
 };

@@ -10,7 +10,10 @@ namespace b200pt {
 
 constexpr int kPathScalars = 16;  // lambdaU, etaScale, pB, prev{pi.lo, pi.hi, n, ns}, cameraWeight
 constexpr int kCameraWeightScalar = 15;  // written by the generate kernel, read when the sample is finished
-constexpr int kPathInts = 4;      // sampleIndex, dimension, depth, flags
+constexpr int kPathInts = 5;      // sampleIndex, dimension, depth, flags, medium
+constexpr int kShadowAuxWords = 20;  // volpath light sample: p_l, scatterPDF, medium, started, rng[4], lightPi[6], lightN[3]
+constexpr uint32_t kConsumedTag = 0xFFFFFFFDu;  // hit slot of a ray the medium kernel already dealt with
+constexpr int kVolMaxIterations = 96;  // wavefront iterations of a volpath pass (interfaces do not count as depth)
 constexpr int kMatQueues = 4;     // one shading queue per MaterialType
 constexpr int kCountStride = 8;   // ints per depth in PassBuffers::counts
 
@@ -37,13 +40,20 @@ struct PassBuffers {
     int *shPath;           // n     path id, -1 = void slot
     float *Ld;             // 31 x n  contribution to add when unoccluded (already x beta)
     unsigned char *occluded;  // n
+    // ---- volpath only (null otherwise): rescaled path probabilities per path, the transmittance walk's state per
+    // shadow-queue slot, closest hits of the shadow rays, number of walks that go on to another segment
+    float *ru, *rl;        // 31 x n
+    float *shT, *shRl, *shRu;  // 31 x n
+    uint32_t *shAux;       // n x kShadowAuxWords
+    uint32_t *shHits;      // n x 6
+    int *shContinue;       // 1
     // ---- queue lengths: counts[kCountStride * depth + {0 rays, 1 shadow, 2.. material queues}]
     int *counts;
     int maxDepthSlots;
 };
 
-size_t PassBufferBytes(long long n, int depthSlots);
-void CarvePassBuffers(void *base, long long n, int depthSlots, PassBuffers &pb);
+size_t PassBufferBytes(long long n, int depthSlots, bool vol);
+void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuffers &pb);
 
 cudaError_t LaunchGenerate(const RenderSceneDev &rs, const PassBuffers &pb, int nPixels, int width, int nActive,
                            int firstSample, int sampleStride, cudaStream_t stream);
@@ -52,6 +62,11 @@ cudaError_t LaunchClassify(const RenderSceneDev &rs, const PassBuffers &pb, int 
 // matMask: bit m set = material type m occurs in the scene (its queue is shaded)
 cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width,
                         int nActive, uint32_t matMask, cudaStream_t stream, int *launches);
+// volpath: delta tracking of the rays that travel in a medium (before classify), one segment of every light
+// sample's transmittance walk (after a closest-hit pass over the shadow rays into pb.shHits)
+cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width, int nActive,
+                            cudaStream_t stream);
+cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream);
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream);
 cudaError_t LaunchFinish(const RenderSceneDev &rs, const PassBuffers &pb, int nActive, cudaStream_t stream);
 cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream);

@@ -36,6 +36,7 @@ struct PathRegs {
     int px, py, sampleIndex, dimension, depth;
     uint32_t flags;
     float etaScale, pB, filterWeight;
+    int medium;          // Ray::medium of p.ray, index into the scene's media, -1 = none (volpath only)
     float cameraWeight;  // CameraRay::weight: L = weight * Li (cpu/integrators.cpp:247-252); 0 = no ray
     LightCtx prev;
     V3 rayO, rayD;
@@ -92,6 +93,7 @@ B2_HD void GenerateCameraPath(const RenderSceneDev &rs, PathRegs &p, int px, int
     }
     p.etaScale = 1.f;
     p.pB = 0.f;
+    p.medium = rs.integrator.type == 1 ? rs.camera.medium : -1;
     p.prev.pi.lo = p.prev.pi.hi = p.prev.n = p.prev.ns = mk(0, 0, 0);
 }
 
@@ -196,6 +198,46 @@ B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval
     return 0.f;
 }
 
+// What a light sample needs beyond its ray when media are present (SampleLd's state before the walk,
+// cpu/integrators.cpp:1296-1332)
+struct ShadowVolInfo {
+    float p_l, scatterPDF;
+    int medium;   // medium of the ray's first segment, -1 = none
+    P3i lightPi;  // ls->pLight: the walk re-aims at it after every interface (SpawnRayTo)
+    V3 lightN;
+};
+
+// Sum of r_u over the wavelengths / N (SampledSpectrum::Average), and of r_u + r_l
+template <class IO>
+B2_HD float AvgRu(const IO &io) {
+    float sum = io.Ru(0);
+    for (int k = 1; k < kNLambda; ++k) sum += io.Ru(k);
+    return sum / kNLambda;
+}
+template <class IO>
+B2_HD float AvgRuRl(const IO &io) {
+    float sum = io.Ru(0) + io.Rl(0);
+    for (int k = 1; k < kNLambda; ++k) sum += io.Ru(k) + io.Rl(k);
+    return sum / kNLambda;
+}
+
+// VolPathIntegrator's escaped ray (cpu/integrators.cpp:1081-1099): beta * Le / r_u.Average(); with MIS r_l is first
+// scaled by the light's p_l, which is 0 for a UniformInfiniteLight under allowIncompletePDF, so the weight is the same.
+template <class IO>
+B2_HD void EscapedRadianceVol(const RenderSceneDev &rs, float lambdaU, IO &io) {
+    const float avg = AvgRu(io);
+    for (uint32_t i = 0; i < rs.nInfiniteLights; ++i) {
+        const LightDev &light = rs.lights[rs.infiniteLights[i]];
+        const SpectrumTable &sp = rs.spectra[light.spectrum];
+        LambdaIter li(lambdaU);
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+            float Le = light.scale * SpectrumAt(sp, li.lam);
+            if (Le != 0) io.AddL(k, io.Beta(k) * Le / avg);
+        }
+    }
+}
+
 // Escaped ray: every infinite light adds beta * Le, MIS-weighted against light sampling unless the ray
 // left the camera or a specular bounce (cpu/integrators.cpp:645-662).  UniformInfiniteLight::PDF_Li is 0
 // under allowIncompletePDF (lights.cpp:998-1003), so the weight is PowerHeuristic(p_b, 0).
@@ -220,11 +262,20 @@ B2_SPECTRAL_LOOP
 // path throughput.
 // MAT / LBVH: material type and "the light sampler is the BVH one" fixed at compile time (the kernels);
 // -1 = read from the scene (the host check).
-template <class IO, int MAT = -1, int LBVH = -1>
+// VOL: 1 = the surface half of VolPathIntegrator::Li (cpu/integrators.cpp:1100-1268): MIS through the rescaled path
+// probabilities r_u / r_l (IO::Ru / Rl), interface surfaces are crossed, light samples carry what the
+// transmittance walk needs (IO::ShadowEndVol), the ray's medium follows the surface's MediumInterface.
+template <class IO, int MAT = -1, int LBVH = -1, int VOL = -1>
 B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit[6], IO &io) {
     const bool lightBvh = LBVH < 0 ? rs.integrator.lightSampler == 2 : LBVH == 1;
+    const bool vol = VOL < 0 ? rs.integrator.type == 1 : VOL == 1;
     if (hit[0] == kMissTag) {  // escaped ray (cpu/integrators.cpp:645-662); the kernels do this in ClassifyKernel
-        if (rs.nInfiniteLights) EscapedRadiance(rs, p.lambdaU, p.depth == 0 || (p.flags & PF_SPECULAR), p.pB, io);
+        if (rs.nInfiniteLights) {
+            if (vol)
+                EscapedRadianceVol(rs, p.lambdaU, io);
+            else
+                EscapedRadiance(rs, p.lambdaU, p.depth == 0 || (p.flags & PF_SPECULAR), p.pB, io);
+        }
         KillPath(p);
         return;
     }
@@ -254,7 +305,34 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
     // ---- emitted light at the hit (cpu/integrators.cpp:664-679)
     if (mesh.lightFirst >= 0) {
         const LightDev al = rs.lights[mesh.lightFirst + tv.tri];
-        if (AreaLightEmits(al, si.n, wo)) {
+        if (vol && AreaLightEmits(al, si.n, wo)) {  // cpu/integrators.cpp:1102-1115
+            const SpectrumTable &sp = rs.spectra[al.spectrum];
+            bool anyLe = false;
+            {
+                LambdaIter li(p.lambdaU);
+B2_SPECTRAL_LOOP
+                for (int k = 0; k < kNLambda; ++k, li.Next()) anyLe |= al.scale * SpectrumAt(sp, li.lam) != 0;
+            }
+            if (anyLe) {
+                float avg;
+                if (p.depth == 0 || (p.flags & PF_SPECULAR))
+                    avg = AvgRu(io);
+                else {
+                    float pmf = al.aliasP;
+                    if (rs.integrator.lightSampler == 0) pmf = 1.f / rs.nLights;
+                    if (lightBvh) pmf = LightBvhPMF(rs, Mid(p.prev.pi), p.prev.ns, mesh.lightFirst + (int)tv.tri);
+                    float p_l = pmf * TrianglePDF(tv, p.prev, p.rayD, al.flipNormal != 0);
+                    for (int k = 0; k < kNLambda; ++k) io.SetRl(k, io.Rl(k) * p_l);
+                    avg = AvgRuRl(io);
+                }
+                LambdaIter li(p.lambdaU);
+B2_SPECTRAL_LOOP
+                for (int k = 0; k < kNLambda; ++k, li.Next()) {
+                    float Le = al.scale * SpectrumAt(sp, li.lam);
+                    io.AddL(k, io.Beta(k) * Le / avg);
+                }
+            }
+        } else if (AreaLightEmits(al, si.n, wo)) {
             float w = 1.f;
             if (!(p.depth == 0 || (p.flags & PF_SPECULAR))) {
                 float pmf = al.aliasP;  // PowerLightSampler::PMF (lightsamplers.h:78-82)
@@ -275,8 +353,15 @@ B2_SPECTRAL_LOOP
     }
 
     // ---- BSDF
-    if (mesh.material < 0) {  // interface material: skip the surface (cpu/integrators.cpp:683-688); not used yet
-        KillPath(p);
+    if (mesh.material < 0) {  // interface material: isect.SkipIntersection(&ray, tHit) and go on (:1118-1122)
+        if (!vol) {
+            KillPath(p);
+            return;
+        }
+        p.rayO = OffsetRayOrigin(si.pi, si.n, p.rayD);  // SpawnRay(ray->d)
+        p.rayTMax = INFINITY;
+        p.medium = mesh.mediumInside == mesh.mediumOutside ? p.medium
+                                                           : (DotN(si.n, p.rayD) > 0 ? mesh.mediumOutside : mesh.mediumInside);
         return;
     }
     const MaterialDev mat = rs.materials[mesh.material];
@@ -370,14 +455,26 @@ B2_SPECTRAL_LOOP
                         for (int k = 0; k < kNLambda; ++k, li.Next()) {
                             float Le = light.scale * SpectrumAt(sp, li.lam) * atten;
                             float f = BsdfSpectral(rs, bsdf, ev, li.lam) * absCos;
-                            io.SetLd(k, io.Beta(k) * (w_l * Le * f / p_l));
+                            // volpath keeps beta * f_hat * L; the transmittance walk supplies T_ray and the MIS weight
+                            io.SetLd(k, vol ? io.Beta(k) * f * Le : io.Beta(k) * (w_l * Le * f / p_l));
                             anyL |= Le != 0;
                             anyF |= f != 0;
                         }
                         // Unoccluded(intr, ls->pLight): intr.SpawnRayTo(pLight) (ray.h:106-111), tMax 1 - ShadowEpsilon
                         V3 pf = OffsetRayOrigin(si.pi, si.n, Mid(ss.pi) - Mid(si.pi));
                         V3 pt = OffsetRayOrigin(ss.pi, ss.n, pf - Mid(ss.pi));
-                        io.ShadowEnd(anyL && anyF, pf, pt - pf, 1 - kShadowEpsilon);
+                        if (vol) {
+                            ShadowVolInfo info;
+                            info.p_l = p_l;
+                            info.scatterPDF = p_b;
+                            info.medium = mesh.mediumInside == mesh.mediumOutside
+                                              ? p.medium
+                                              : (DotN(si.n, pt - pf) > 0 ? mesh.mediumOutside : mesh.mediumInside);
+                            info.lightPi = ss.pi;
+                            info.lightN = ss.n;
+                            io.ShadowEndVol(anyL && anyF, pf, pt - pf, 1 - kShadowEpsilon, info);
+                        } else
+                            io.ShadowEnd(anyL && anyF, pf, pt - pf, 1 - kShadowEpsilon);
                     }
                 }
             }
@@ -420,6 +517,11 @@ B2_SPECTRAL_LOOP
         return;
     }
     p.pB = bs.pdfIsProportional ? EvalPDF(bsdf, woL, bs.wi) : bs.pdf;
+    if (vol) {  // r_l = r_u / pdf (cpu/integrators.cpp:1190-1193); the ray's medium follows the surface's interface
+        for (int k = 0; k < kNLambda; ++k) io.SetRl(k, io.Ru(k) / p.pB);
+        p.medium = mesh.mediumInside == mesh.mediumOutside ? p.medium
+                                                           : (DotN(si.n, wi) > 0 ? mesh.mediumOutside : mesh.mediumInside);
+    }
     bool specular = (bs.flags & BX_SPECULAR) != 0;
     p.flags = specular ? (p.flags | PF_SPECULAR) : ((p.flags & ~PF_SPECULAR) | PF_ANY_NONSPECULAR);
     if (bs.flags & BX_TRANSMISSION) p.etaScale *= SqrF(bs.eta);
@@ -430,7 +532,25 @@ B2_SPECTRAL_LOOP
     p.rayD = wi;
     p.rayTMax = INFINITY;
 
-    // ---- Russian roulette (cpu/integrators.cpp:748-756)
+    // ---- Russian roulette (cpu/integrators.cpp:748-756; volpath :1255-1266: rrBeta = beta * etaScale /
+    // r_u.Average(), and uRR is drawn whether or not it is used)
+    if (vol) {
+        const float avg = AvgRu(io);
+        float mc = io.Beta(0) * p.etaScale / avg;
+        for (int k = 1; k < kNLambda; ++k) mc = fmaxf(mc, io.Beta(k) * p.etaScale / avg);
+        s = SamplerFor(rs, p);
+        float uRR = ZSobolGet1D(s);
+        p.dimension = s.dimension;
+        if (mc < 1 && p.depth > 1) {
+            float q = fmaxf(0.f, 1 - mc);
+            if (uRR < q) {
+                KillPath(p);
+                return;
+            }
+            for (int k = 0; k < kNLambda; ++k) io.SetBeta(k, io.Beta(k) / (1 - q));
+        }
+        return;
+    }
     float maxComp = io.Beta(0) * p.etaScale;
 B2_SPECTRAL_LOOP
     for (int k = 1; k < kNLambda; ++k) maxComp = fmaxf(maxComp, io.Beta(k) * p.etaScale);
@@ -527,3 +647,5 @@ B2_SPECTRAL_LOOP
 }
 
 }  // namespace b200pt
+
+#include "render_volpath.h"

@@ -49,6 +49,21 @@ struct MeshAttrDev {
     int32_t lightFirst;  // light index of triangle 0 of this mesh, -1 if not emissive
     uint32_t flipNormal;
     uint32_t pad;
+    int32_t mediumInside, mediumOutside;  // MediumInterface; equal = no transition (the ray keeps its medium)
+};
+
+// One participating medium (media.h:217-345): homogeneous, or a density grid with its majorant grid.
+struct MediumDev {
+    uint32_t type;              // 0 homogeneous, 1 grid
+    int32_t sigmaA, sigmaS;     // spectrum tables (nearest lookup, already scaled)
+    float g;                    // Henyey-Greenstein asymmetry
+    float bounds[6];            // grid: medium-space bounds
+    float mediumFromRender[16];
+    float renderFromMedium[16];
+    int32_t nx, ny, nz;
+    int32_t mres[3];
+    const float *density;
+    const float *majorants;
 };
 
 struct CameraDev {
@@ -63,6 +78,7 @@ struct CameraDev {
     int32_t nLens, nPupilBounds;
     float physicalExtent[4];     // Bounds2f {pMin.x, pMin.y, pMax.x, pMax.y}
     float filmDiagonal;
+    int32_t medium;              // medium camera rays start in, -1 = none
 };
 
 struct FilmDev {
@@ -91,6 +107,7 @@ struct IntegratorDev {
     int32_t maxDepth;
     uint32_t regularize;
     uint32_t lightSampler;       // 0 uniform, 1 power, 2 bvh
+    uint32_t type;               // 0 path (cpu/integrators.cpp:629-805), 1 volpath (:953-1405)
 };
 
 struct RenderSceneDev {
@@ -111,6 +128,8 @@ struct RenderSceneDev {
     const int32_t *infiniteLights;
     uint32_t nLightBvhNodes, nInfiniteLights;
     float lightBvhBounds[6];
+    const MediumDev *media;
+    uint32_t nMedia;
 };
 
 // Per-path state, structure of arrays over `n` paths of a pass.  Spectral arrays are [k][path].

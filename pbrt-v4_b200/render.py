@@ -108,6 +108,30 @@ class RenderScene:
         r.n_spectra, r.n_materials, r.n_lights, r.n_meshes = ns, nm, nl, nme
         r.spectra, r.materials, r.lights, r.meshes = spectra, mats, lights, meshes
         keep += [spectra, mats, lights, meshes]
+        r.integrator_type = int(d["integrator_type"][0]) if "integrator_type" in d else 0
+        r.camera_medium = -1
+        if r.integrator_type == 1:  # VolPathIntegrator: media, medium interfaces, camera medium
+            mi, mf = d["media_i"].reshape(-1, 9), d["media_f"].reshape(-1, 39)
+            media = (capi.Medium * max(len(mi), 1))()
+            for k in range(len(mi)):
+                m = media[k]
+                m.type, m.sigma_a, m.sigma_s = int(mi[k][0]), int(mi[k][1]), int(mi[k][2])
+                m.nx, m.ny, m.nz = (int(x) for x in mi[k][3:6])
+                m.mres[:] = [int(x) for x in mi[k][6:9]]
+                m.g = float(mf[k][0])
+                m.bounds[:] = [float(x) for x in mf[k][1:7]]
+                m.medium_from_render[:] = [float(x) for x in mf[k][7:23]]
+                m.render_from_medium[:] = [float(x) for x in mf[k][23:39]]
+                if m.type == 1:
+                    dens = np.ascontiguousarray(d[f"medium_density_{k}"], np.float32).reshape(-1)
+                    maj = np.ascontiguousarray(d[f"medium_majorants_{k}"], np.float32).reshape(-1)
+                    m.density, m.majorants = capi.fptr(dens), capi.fptr(maj)
+                    keep += [dens, maj]
+            mm = np.ascontiguousarray(d["mesh_media"], np.int32).reshape(-1)
+            r.n_media, r.media = len(mi), media
+            r.mesh_media = mm.ctypes.data_as(C.POINTER(C.c_int32))
+            r.camera_medium = int(d["camera_medium"][0])
+            keep += [media, mm]
         if r.light_sampler == 2:  # BVHLightSampler tables
             nodes = np.ascontiguousarray(d["lightbvh_nodes"], np.uint32)
             trails = np.ascontiguousarray(d["lightbvh_trails"], np.uint32)

@@ -543,6 +543,113 @@ def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0,
     return sc
 
 
+def procedural_density(n=256, seed=7):
+    """n^3 density in [0, 1]: three octaves of value noise (hash lattice, trilinear) shaped into a ball that
+    fades out towards the grid's faces; x fastest, as SampledGrid stores it (util/containers.h:826)."""
+    rng = np.random.default_rng(seed)
+    t = (np.arange(n, dtype=np.float32) + 0.5) / n
+    out = np.zeros((n, n, n), np.float32)
+    amp = 1.0
+    for cells in (4, 8, 16):
+        lat = rng.random((cells + 1,) * 3, dtype=np.float32)
+        x = t * cells
+        i = np.minimum(x.astype(np.int32), cells - 1)
+        f = (x - i).astype(np.float32)
+        f = f * f * (3 - 2 * f)
+        def ax(a, axis):
+            sh = [1, 1, 1]
+            sh[axis] = n
+            lo, hi = np.take(a, i, axis=axis), np.take(a, i + 1, axis=axis)
+            return lo + (hi - lo) * f.reshape(sh)
+        out += amp * ax(ax(ax(lat, 0), 1), 2)
+        amp *= 0.5
+    out /= 1.75
+    z, y, x = np.meshgrid(t, t, t, indexing="ij")
+    r = np.sqrt((x - 0.5) ** 2 + (y - 0.5) ** 2 + (z - 0.5) ** 2)
+    out = np.clip((out - 0.25) * 2.2, 0, 1) * np.clip((0.5 - r) * 6, 0, 1)
+    return np.ascontiguousarray(out.astype(np.float32))
+
+
+def majorant_grid(density, res=16):
+    """MajorantGrid of GridMedium's constructor (media.cpp:240-246) over SampledGrid::MaxValue
+    (util/containers.h:836-853): per voxel of a res^3 grid, the max of the density samples whose trilinear
+    support overlaps it."""
+    nz, ny, nx = density.shape
+    out = np.zeros((res, res, res), np.float32)
+    def rng_(k, n):
+        f32 = np.float32
+        lo = int(np.floor(f32(f32(k) / f32(res)) * f32(n) - f32(0.5)))
+        hi = int(np.floor(f32(f32(k + 1) / f32(res)) * f32(n) - f32(0.5)))
+        return max(lo, 0), min(hi + 1, n - 1)
+    for z in range(res):
+        z0, z1 = rng_(z, nz)
+        for y in range(res):
+            y0, y1 = rng_(y, ny)
+            for x in range(res):
+                x0, x1 = rng_(x, nx)
+                out[z, y, x] = density[z0:z1 + 1, y0:y1 + 1, x0:x1 + 1].max()
+    return out
+
+
+def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm", seed=0, grid=256, density=None,
+                 fog=True, crop=None, lightsampler="bvh"):
+    """BASELINE configs[4]: VolPathIntegrator in the Cornell room: a thin homogeneous fog fills the room (an
+    `interface` quad closes the open front; the camera stays in vacuum: a camera medium trips a race in the
+    reference's BasicScene::GetMedium / CreateMedia, scene.cpp:809-850), and a box-shaped `interface` shell
+    holds a "uniformgrid" medium with a procedural grid^3 density (procedural_density); ceiling area light."""
+    sc = cornell_box()
+    white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
+    colours = [white, white, white, red, green, None, white, None]  # the short box stays, the tall one makes room
+    dens = procedural_density(grid) if density is None else density
+    nz, ny, nx = dens.shape
+    cropw = f' "float cropwindow" [{crop[0]} {crop[1]} {crop[2]} {crop[3]}]' if crop else ''
+    lines = ['LookAt 0.5 0.5 -1.4  0.5 0.5 0.5  0 1 0']
+    lines += [
+        'Camera "perspective" "float fov" 39.3',
+        f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
+        f'Integrator "volpath" "integer maxdepth" {maxdepth} "string lightsampler" "{lightsampler}"',
+        'PixelFilter "box"',
+        f'Film "rgb" "string filename" "{out}" "integer xresolution" {res[0]} "integer yresolution" {res[1]} '
+        '"bool savefp16" false' + cropw,
+        'WorldBegin',
+    ]
+    outside = '"fog"' if fog else '""'
+    if fog:
+        lines += ['MakeNamedMedium "fog" "string type" "homogeneous" "rgb sigma_a" [0.02 0.02 0.03] '
+                  '"rgb sigma_s" [0.25 0.25 0.3] "float scale" 1 "float g" 0.3',
+                  # front cap, normal towards the camera (-z): fog behind it, vacuum in front
+                  'AttributeBegin', '  MediumInterface "fog" ""', '  Material "interface"',
+                  '  ' + _mesh_pbrt(_quad([0, 0, 0], [0, 1, 0], [1, 1, 0], [1, 0, 0])), 'AttributeEnd']
+    lo, hi = (0.22, 0.18, 0.25), (0.78, 0.74, 0.81)
+    lines.append(f'MakeNamedMedium "cloud" "string type" "uniformgrid" "integer nx" {nx} "integer ny" {ny} "integer nz" {nz} '
+                 f'"point3 p0" [{lo[0]} {lo[1]} {lo[2]}] "point3 p1" [{hi[0]} {hi[1]} {hi[2]}] '
+                 '"rgb sigma_a" [0.5 0.5 0.5] "rgb sigma_s" [14 14 15] "float scale" 1 "float g" 0.6 "float density" [')
+    flat = dens.reshape(-1)
+    for k in range(0, len(flat), 65536):
+        lines.append(" ".join(f"{v:.6g}" for v in flat[k:k + 65536]))
+    lines.append(']')
+    for m, c in zip(sc.meshes, colours):
+        if c is None and m is not sc.meshes[5]:
+            continue
+        lines.append('AttributeBegin')
+        if c is None:
+            lines.append('  AreaLightSource "diffuse" "rgb L" [17 12 4]')
+            lines.append('  Material "diffuse" "rgb reflectance" [0 0 0]')
+        else:
+            lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
+        lines.append('  ' + _mesh_pbrt(m))
+        lines.append('AttributeEnd')
+    # the shell: interface material (no BSDF), cloud inside, fog (or vacuum) outside; slightly larger than
+    # the grid's box so every ray segment inside the shell sees the whole grid
+    e = 0.004
+    shell = _box((lo[0] - e, lo[1] - e, lo[2] - e), (hi[0] + e, hi[1] + e, hi[2] + e))
+    lines += ['AttributeBegin', f'  MediumInterface "cloud" {outside}', '  Material "interface"',
+              '  ' + _mesh_pbrt(shell), 'AttributeEnd']
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return sc
+
+
 def load_b2rs(path):
     """Reads the named-array container written by a host adaptor (oracle/dumpscene_ref.cpp is the
     test-side one): 'B2RS', u32 count, {u32 nameLen, name, u32 dtype, u32 ndim, u32 dims[], data}."""

@@ -104,6 +104,26 @@ def make_config4_goldens(P, refrun, out):
         print("config4_small", img.shape, names[:4], "mean", img[..., :3].mean(axis=(0, 1)), f"{secs:.2f}s")
 
 
+# BASELINE.json configs[4] (scenes.config5_pbrt): VolPathIntegrator, homogeneous fog + a grid medium inside an
+# interface shell.  In miniature (24^3 density) with the reference's image at two seeds; the full-size tables
+# (256^3 density, 1920x1080, 512 spp) are derived from the small ones by bench.py (the grid alone is 67 MB).
+CONFIG5_FULL = dict(res=(1920, 1080), spp=512, maxdepth=5, grid=256)
+CONFIG5_SMALL = dict(res=(64, 48), spp=16, maxdepth=5, grid=24)
+
+
+def make_config5_goldens(P, refrun, out):
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt, pfm = os.path.join(tmp, "c5.pbrt"), os.path.join(tmp, "c5.pfm")
+        for seed, suffix in ((0, "_ref.npy"), (1, "_ref2.npy")):
+            P.scenes.config5_pbrt(pbrt, out=pfm, seed=seed, **CONFIG5_SMALL)
+            if seed == 0:
+                refrun.dump_scene(pbrt, os.path.join(out, "config5_small.b2rs"))
+            img, secs = refrun.render(pbrt, pfm)
+            np.save(os.path.join(out, "config5_small" + suffix), img.astype(np.float32))
+        print("config5_small", img.shape, "mean", img.mean(axis=(0, 1)))
+
+
 def make_render_goldens(P, refrun, out):
     import tempfile
     for name, kw in RENDER_CASES.items():
@@ -145,11 +165,15 @@ if __name__ == "__main__":
     import pbrt_v4_b200 as P
     import refrun
     out = os.path.dirname(os.path.abspath(__file__))
+    if "--config5-only" in sys.argv:
+        make_config5_goldens(P, refrun, out)
+        sys.exit(0)
     if "--config4-only" in sys.argv:
         make_config4_goldens(P, refrun, out)
         sys.exit(0)
     make_render_goldens(P, refrun, out)
     make_config4_goldens(P, refrun, out)
+    make_config5_goldens(P, refrun, out)
     if "--render-only" in sys.argv:
         sys.exit(0)
     for name, (sc, rays) in cases(P.scenes).items():

@@ -33,6 +33,16 @@ bool Trace(const HostScene &hs, V3 o, V3 d, float tMax, bool any, uint32_t hit[6
 // the IO of ShadeVertex on the host: plain arrays, shadow ray resolved right after the vertex
 struct HostIO {
     float L[kNLambda], Ld[kNLambda], beta[kNLambda];
+    float ru[kNLambda], rl[kNLambda];  // volpath: rescaled path probabilities
+    ShadowVolInfo info;
+    float Ru(int k) const { return ru[k]; }
+    void SetRu(int k, float v) { ru[k] = v; }
+    float Rl(int k) const { return rl[k]; }
+    void SetRl(int k, float v) { rl[k] = v; }
+    void ShadowEndVol(bool valid, V3 o, V3 d, float tMax, const ShadowVolInfo &i) {
+        ShadowEnd(valid, o, d, tMax);
+        info = i;
+    }
     bool shadow;
     V3 shO, shD;
     float shTMax;
@@ -48,6 +58,50 @@ struct HostIO {
         shTMax = tMax;
     }
 };
+
+// One pixel sample through the host+device path functions: the depth loop of the kernels, one path at a time.
+void RunPath(const RenderSceneDev &rs, const HostScene &hs, PathRegs &p, HostIO &io) {
+    const bool vol = rs.integrator.type == 1;
+    for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f, io.beta[i] = io.ru[i] = io.rl[i] = 1.f;
+    while (p.flags & PF_ALIVE) {
+        uint32_t hit[6] = {kMissTag, 0, 0, 0, 0, 0};
+        Trace(hs, p.rayO, p.rayD, p.rayTMax, false, hit);
+        io.shadow = false;
+        int r = VOL_SURVIVE;
+        if (vol && p.medium >= 0) {
+            float tHit = INFINITY;
+            if (hit[0] != kMissTag) memcpy(&tHit, &hit[1], 4);
+            r = VolMediumStep(rs, p, tHit, io);
+            if (r == VOL_TERMINATED) KillPath(p);
+        }
+        if (r == VOL_SURVIVE) ShadeVertex(rs, p, hit, io);
+        if (!io.shadow) continue;
+        if (!vol) {
+            if (!Trace(hs, io.shO, io.shD, io.shTMax, true, nullptr))
+                for (int i = 0; i < kNLambda; ++i) io.L[i] += io.Ld[i];
+            continue;
+        }
+        // SampleLd's transmittance walk (cpu/integrators.cpp:1329-1395)
+        ShadowRegs sh;
+        sh.o = io.shO;
+        sh.d = io.shD;
+        sh.medium = io.info.medium;
+        sh.rng = PcgSeed(Hash3f(sh.o.x, sh.o.y, sh.o.z), Hash3f(sh.d.x, sh.d.y, sh.d.z));
+        sh.lightPi = io.info.lightPi;
+        sh.lightN = io.info.lightN;
+        float T[kNLambda], rl[kNLambda], ru[kNLambda];
+        for (int i = 0; i < kNLambda; ++i) T[i] = rl[i] = ru[i] = 1.f;
+        int res;
+        do {
+            uint32_t sh_hit[6] = {kMissTag, 0, 0, 0, 0, 0};
+            Trace(hs, sh.o, sh.d, io.shTMax, false, sh_hit);
+            res = ShadowTrSegment(rs, p.lambdaU, sh, sh_hit, T, rl, ru);
+        } while (res == SHADOW_CONTINUE);
+        if (res == SHADOW_REACHED)
+            ShadowTrFinish(T, rl, ru, io.info.p_l, io.info.scatterPDF, [&](int k) { return io.Ld[k]; },
+                           [&](int k) { return io.ru[k]; }, [&](int k, float v) { io.L[k] += v; });
+    }
+}
 
 }  // namespace
 
@@ -76,6 +130,11 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
     rs.camera.pupilBounds = rh.pupilBounds.data();
+    for (size_t i = 0; i < rh.media.size(); ++i) {
+        rh.media[i].density = rh.mediumGrids[i].first.data();
+        rh.media[i].majorants = rh.mediumGrids[i].second.data();
+    }
+    rs.media = rh.media.data();
     const int W = rh.width, H = rh.height;
     if (nThreads < 1) nThreads = 1;
     std::vector<std::thread> pool;
@@ -87,16 +146,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
                         PathRegs p;
                         GenerateCameraPath(rs, p, rs.film.x0 + x, rs.film.y0 + y, firstSample + k * stride);
                         HostIO io;
-                        for (int i = 0; i < kNLambda; ++i) io.L[i] = 0.f, io.beta[i] = 1.f;
-                        // depth loop: one closest-hit + one shadow ray per vertex, as the kernels do
-                        while (p.flags & PF_ALIVE) {
-                            uint32_t hit[6] = {kMissTag, 0, 0, 0, 0, 0};
-                            Trace(hs, p.rayO, p.rayD, p.rayTMax, false, hit);
-                            io.shadow = false;
-                            ShadeVertex(rs, p, hit, io);
-                            if (io.shadow && !Trace(hs, io.shO, io.shD, io.shTMax, true, nullptr))
-                                for (int i = 0; i < kNLambda; ++i) io.L[i] += io.Ld[i];
-                        }
+                        RunPath(rs, hs, p, io);
                         float out[4];
                         const float cw = p.cameraWeight;
                         FinishPath(rs, p.lambdaU, p.flags, p.filterWeight, [&](int i) { return cw * io.L[i]; }, out);
@@ -138,6 +188,11 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
     rs.camera.pupilBounds = rh.pupilBounds.data();
+    for (size_t i = 0; i < rh.media.size(); ++i) {
+        rh.media[i].density = rh.mediumGrids[i].first.data();
+        rh.media[i].majorants = rh.mediumGrids[i].second.data();
+    }
+    rs.media = rh.media.data();
     int full = rs.integrator.maxDepth;
     for (int d = 0; d <= full; ++d) {
         rs.integrator.maxDepth = d;

@@ -158,3 +158,26 @@ def test_realistic_camera_description_is_validated(P, rendercheck):
     d["camera_lens"][0, 2] = 0.0  # a curved element with eta 0
     with pytest.raises(AssertionError, match="eta 0"):
         rendercheck(P.RenderScene(d))
+
+
+def test_golden_image_config5_volpath(P, rendercheck):
+    """BASELINE configs[4] in miniature: VolPathIntegrator (cpu/integrators.cpp:953-1405) through a homogeneous
+    fog and a grid medium inside an interface shell: delta tracking over the majorant grid, real / null
+    collisions with the r_u / r_l path probabilities, light samples whose transmittance walk crosses interfaces.
+    The sampler dimensions and both RNG streams are the reference's, so paths follow the reference's; the gate is
+    the noise floor, and the measured distance has to stay a small fraction of it."""
+    name = "config5_small"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref, ref2 = (np.load(os.path.join(GOLD, name + s)) for s in ("_ref.npy", "_ref2.npy"))
+    assert int(rsc.d["integrator_type"][0]) == 1 and len(rsc.d["media_i"]) == 2
+    img = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
+    ok, floor = noise_gate(img, ref, ref2)
+    assert ok, (rrmse(img, ref), floor)
+    assert rrmse(img, ref) <= 0.01 * floor
+    assert abs(img.mean() - ref.mean()) <= TOL_MEAN * ref.mean()
+
+
+def test_majorant_grid_mirror(P):
+    """scenes.majorant_grid (used to build full-size config-5 tables) reproduces the host's MajorantGrid."""
+    d = P.scenes.load_b2rs(os.path.join(GOLD, "config5_small.b2rs"))
+    np.testing.assert_array_equal(P.scenes.majorant_grid(d["medium_density_0"]), d["medium_majorants_0"])

@@ -197,3 +197,24 @@ def test_config4_realistic_camera_spectral(P, rendercheck):
     np.testing.assert_array_equal(rgbw[..., 3], float(rsc.spp))
     cpu = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
     assert rrmse(img, cpu) <= 1e-4
+
+
+def test_config5_volpath(P, rendercheck):
+    """BASELINE configs[4] in miniature on the device: medium kernel, volumetric shading, transmittance walks."""
+    name = "config5_small"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref, ref2 = (np.load(os.path.join(GOLD, name + s)) for s in ("_ref.npy", "_ref2.npy"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img, film = r.image(), r.film()
+        st = r.stats()
+    finally:
+        r.close()
+    floor = rrmse(ref2, ref)
+    assert np.all(film[..., 3] == rsc.spp)
+    assert rrmse(img, ref) <= 0.05 * floor, (rrmse(img, ref), floor)
+    assert abs(img.mean() - ref.mean()) <= 1e-3 * ref.mean()
+    cpu = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
+    assert rrmse(img, cpu) <= 0.05 * floor
+    assert st["shadow_rays"] > 0
