@@ -48,6 +48,11 @@ def parse():
     ap.add_argument("--no-config4", action="store_true", help="skip the config-4 (realistic lens + spectral film) section")
     ap.add_argument("--config4-spp", type=int, default=64, help="spp of config 4's frame rendered per step")
     ap.add_argument("--config4-cpu-spp", type=int, default=4, help="spp of the bounded reference sample of config 4")
+    ap.add_argument("--no-config5", action="store_true", help="skip the config-5 (volpath, 256^3 grid medium) section")
+    ap.add_argument("--config5-spp", type=int, default=16, help="spp of config 5's frame rendered per step")
+    ap.add_argument("--config5-grid", type=int, default=256, help="density grid resolution of config 5")
+    ap.add_argument("--config5-cpu-res", type=int, nargs=2, default=[480, 270], help="frame of the bounded reference sample")
+    ap.add_argument("--config5-cpu-spp", type=int, default=4, help="spp of the bounded reference sample of config 5")
     ap.add_argument("--config3-cpu-spp", type=int, default=2, help="spp of the bounded pbrt_ref sample of config 3")
     return ap.parse_args()
 
@@ -472,6 +477,88 @@ def config4_cpu_reference(args, P):
                       f"the whole process incl. parse and the camera's exit-pupil table (64 x 2^20 lens traces)"}
 
 
+CONFIG5_CASE = "config5_full"  # BASELINE.json configs[4]; frame tables in tests/golden, the 256^3 grid is made here
+
+
+def config5_section(args, P, torch, dist, rank, world, local, stream, barrier):
+    """Config 5 end to end: VolPathIntegrator through a homogeneous fog and a --config5-grid^3 density grid inside
+    an interface shell, 1920x1080; --config5-spp of its 512 spp per step, sample stripes over the ranks."""
+    d = P.scenes.load_b2rs(os.path.join(ROOT, "tests", "golden", CONFIG5_CASE + ".b2rs"))
+    rsc = P.RenderScene(P.scenes.with_density_grid(d, P.scenes.procedural_density(args.config5_grid)))
+    spp = min(args.config5_spp, rsc.spp)
+    r = P.B200Renderer(rsc, device=local, stream=stream.cuda_stream)
+    ptr, nd = r.film_device_ptr()
+    film_t = torch.as_tensor(_DevArray(ptr, nd, "<f8"), device="cuda")
+
+    def frame(read):
+        r.clear()
+        r.render(*P.parallel.sample_stripe(spp, rank, world))
+        P.parallel.reduce_film(film_t, dist)
+        return r.image() if (read and rank == 0) else None
+
+    for _ in range(min(args.warmup, 3)):
+        frame(False)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        frame(False)
+    e1.record(stream)
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    st = r.stats()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        img = frame(True)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    r.close()
+    t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_s = (float(x) for x in t.cpu())
+    if rank != 0:
+        return None
+    w, h = rsc.resolution
+    ns = w * h * spp * args.steps
+    g = args.config5_grid
+    out = {"metric": "render_msamples_per_s", "unit": "Msamples/s", "value": ns / (dev_ms * 1e-3) * 1e-6,
+           "ms_per_frame": dev_ms / args.steps, "scaling": "strong",
+           "workload": f"config5: volpath maxdepth 5 in the Cornell room, homogeneous fog + {g}^3 procedural density grid "
+                       f"(16^3 majorants) inside an interface shell, area light, {w}x{h}; {spp} of the frame's {rsc.spp} spp "
+                       f"per step; sample stripes over {world} rank(s), film reduced by NCCL",
+           "e2e": {"value": ns / e2e_s * 1e-6, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": w * h * 12},
+           "rays_per_frame": (st["closest_rays"] + st["shadow_rays"]) * world,
+           "launches_per_frame": st["kernel_launches"], "image_mean": float(img.mean())}
+    if not args.no_cpu_baseline:
+        out["cpu_baseline"] = config5_cpu_reference(args, P)
+    return out
+
+
+def config5_cpu_reference(args, P):
+    """pbrt_ref (CPU VolPathIntegrator) on a bounded sample of config 5: the same scene and grid, a smaller frame at
+    --config5-cpu-spp; the parse of the inline grid (16.7 M values) is timed apart with an 8x8, 1 spp run and
+    subtracted."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refrun
+    if not refrun.render_available():
+        return {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    w, h = args.config5_cpu_res
+    dens = P.scenes.procedural_density(args.config5_grid)
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt, pfm = os.path.join(tmp, "c5.pbrt"), os.path.join(tmp, "c5.pfm")
+        P.scenes.config5_pbrt(pbrt, out=pfm, res=(8, 8), spp=1, grid=args.config5_grid, density=dens)
+        _, setup = refrun.render(pbrt, pfm)
+        P.scenes.config5_pbrt(pbrt, out=pfm, res=(w, h), spp=args.config5_cpu_spp, grid=args.config5_grid, density=dens)
+        _, secs = refrun.render(pbrt, pfm)
+    n = w * h * args.config5_cpu_spp
+    render = max(secs - setup, 1e-3)
+    return {"value": n / render * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
+            "seconds": render, "setup_seconds": setup,
+            "sample": f"the config-5 scene ({args.config5_grid}^3 grid) at {w}x{h}, {args.config5_cpu_spp} spp (config 5 is "
+                      f"1920x1080, 512 spp); wall clock of pbrt_ref minus that of an 8x8 1-spp run (parse + majorant grid)"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU BVHAggregate on all host cores, bounded sample per step."""
     if rank != 0:
@@ -625,6 +712,13 @@ def main():
             agg = None
         config4 = config4_section(args, P, torch, dist, rank, world, local, stream, barrier)
 
+    config5 = None
+    if not args.no_config5:
+        if agg is not None:
+            agg.close()
+            agg = None
+        config5 = config5_section(args, P, torch, dist, rank, world, local, stream, barrier)
+
     # ---- max over ranks
     t = torch.tensor([total_ms, e2e_s, ms_closest, ms_any], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -655,6 +749,7 @@ def main():
             "render": render,
             "config3": config3,
             "config4": config4,
+            "config5": config5,
             "clocks": clk,
             "scene": {"bvh2_nodes": st["n_bvh2_nodes"], "wide_nodes": st["n_wide_nodes"],
                       "device_bytes": st["device_bytes"], "build_s": st["build_seconds"]},

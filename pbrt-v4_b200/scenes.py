@@ -591,6 +591,23 @@ def majorant_grid(density, res=16):
     return out
 
 
+_DENSITY_TEXT = {}
+
+
+def with_density_grid(d, density, medium=0):
+    """A copy of .b2rs tables `d` whose grid medium `medium` holds `density` (nz, ny, nx) and the majorant grid
+    the host would build for it (majorant_grid)."""
+    d = dict(d)
+    density = np.ascontiguousarray(density, np.float32)
+    d[f"medium_density_{medium}"] = density
+    mi = d["media_i"].copy()
+    res = int(mi[medium][6])
+    mi[medium][3:6] = [density.shape[2], density.shape[1], density.shape[0]]
+    d["media_i"] = mi
+    d[f"medium_majorants_{medium}"] = majorant_grid(density, res)
+    return d
+
+
 def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm", seed=0, grid=256, density=None,
                  fog=True, crop=None, lightsampler="bvh"):
     """BASELINE configs[4]: VolPathIntegrator in the Cornell room: a thin homogeneous fog fills the room (an
@@ -624,9 +641,12 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
     lines.append(f'MakeNamedMedium "cloud" "string type" "uniformgrid" "integer nx" {nx} "integer ny" {ny} "integer nz" {nz} '
                  f'"point3 p0" [{lo[0]} {lo[1]} {lo[2]}] "point3 p1" [{hi[0]} {hi[1]} {hi[2]}] '
                  '"rgb sigma_a" [0.5 0.5 0.5] "rgb sigma_s" [14 14 15] "float scale" 1 "float g" 0.6 "float density" [')
-    flat = dens.reshape(-1)
-    for k in range(0, len(flat), 65536):
-        lines.append(" ".join(f"{v:.6g}" for v in flat[k:k + 65536]))
+    key = (dens.shape, hash(dens.tobytes()))
+    if _DENSITY_TEXT.get("key") != key:  # formatting 256^3 values takes ~10 s: keep the last grid's text
+        flat = dens.reshape(-1)
+        _DENSITY_TEXT["key"] = key
+        _DENSITY_TEXT["text"] = "\n".join(" ".join(f"{v:.6g}" for v in flat[k:k + 65536]) for k in range(0, len(flat), 65536))
+    lines.append(_DENSITY_TEXT["text"])
     lines.append(']')
     for m, c in zip(sc.meshes, colours):
         if c is None and m is not sc.meshes[5]:

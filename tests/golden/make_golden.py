@@ -122,6 +122,9 @@ def make_config5_goldens(P, refrun, out):
             img, secs = refrun.render(pbrt, pfm)
             np.save(os.path.join(out, "config5_small" + suffix), img.astype(np.float32))
         print("config5_small", img.shape, "mean", img.mean(axis=(0, 1)))
+        # full-size frame, sampler and integrator tables around the small grid (bench.py swaps the 256^3 grid in)
+        P.scenes.config5_pbrt(pbrt, out=pfm, **dict(CONFIG5_FULL, grid=CONFIG5_SMALL["grid"]))
+        refrun.dump_scene(pbrt, os.path.join(out, "config5_full.b2rs"))
 
 
 def make_render_goldens(P, refrun, out):
