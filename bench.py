@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--no-config5", action="store_true", help="skip the config-5 (volpath, 256^3 grid medium) section")
     ap.add_argument("--config5-spp", type=int, default=16, help="spp of config 5's frame rendered per step")
     ap.add_argument("--config5-grid", type=int, default=256, help="density grid resolution of config 5")
-    ap.add_argument("--config5-cpu-res", type=int, nargs=2, default=[480, 270], help="frame of the bounded reference sample")
+    ap.add_argument("--config5-cpu-res", type=int, nargs=2, default=[960, 540], help="frame of the bounded reference sample")
     ap.add_argument("--config5-cpu-spp", type=int, default=4, help="spp of the bounded reference sample of config 5")
     ap.add_argument("--config3-cpu-spp", type=int, default=2, help="spp of the bounded pbrt_ref sample of config 3")
     return ap.parse_args()
