@@ -226,7 +226,10 @@ def config3_rays(P, rsc, n, seed):
     w, h = rsc.resolution
     cfr = np.asarray(d["camera_from_raster"], np.float64).reshape(4, 4)
     rfc = np.asarray(d["render_from_camera"], np.float64).reshape(4, 4)
-    pf = np.stack([rng.uniform(0, w, n), rng.uniform(0, h, n), np.zeros(n), np.ones(n)], axis=1)
+    # generation order of a wavefront pass (GenerateKernel; wavefront/camera.cpp:32-80): sample after sample, each
+    # in raster order, one jittered position per pixel
+    pix = np.arange(n, dtype=np.int64) % (w * h)
+    pf = np.stack([pix % w + rng.uniform(0, 1, n), pix // w + rng.uniform(0, 1, n), np.zeros(n), np.ones(n)], axis=1)
     pc = pf @ cfr.T
     pc = pc[:, :3] / pc[:, 3:4]
     dirs = pc / np.linalg.norm(pc, axis=1, keepdims=True)
@@ -351,7 +354,7 @@ def config3_section(args, P, torch, dist, rank, world, local, stream, barrier):
                sum(sum(len(m.indices) for m in geo.meshes if m.object == i.object) for i in geo.instances))
     out = {"workload": f"config3: {ntri} instanced triangles ({len(geo.instances)} placements of "
                        f"{len(set(i.object for i in geo.instances))} object definitions), {len(rsc.d['lights_i'])} lights, "
-                       f"{w}x{h}; traversal: {n} camera rays + {n} shadow rays towards emitters per step per rank",
+                       f"{w}x{h}; traversal: {n} camera rays (jittered, in the order a pass generates them: raster order, sample after sample) + {n} shadow rays from their hits towards random emitters per step per rank",
            "triangles": ntri,
            "traversal": {"metric": METRIC, "unit": UNIT,
                          "value": 2 * n * world / ((ms_closest + ms_any) * 1e-3) * 1e-6,

@@ -190,6 +190,32 @@ struct GlobalIO {
     }
 };
 
+// IO of the medium kernel: beta, r_u, r_l staged in shared memory ([k][thread]) for the walk, which updates all
+// three at every tentative collision; light samples go to the shadow queue like DevIO's
+struct MediumIO {
+    const PassBuffers &pb;
+    int path;
+    int *nShadow;
+    int slot;
+    float *sb;  // this thread's column of the block's [3][31][kShadeBlock] shared array
+    __device__ MediumIO(const PassBuffers &b, int pathId, int *shadowCount, float *s)
+        : pb(b), path(pathId), nShadow(shadowCount), slot(-1), sb(s) {}
+    __device__ __forceinline__ float Beta(int k) const { return sb[k * kShadeBlock]; }
+    __device__ __forceinline__ void SetBeta(int k, float v) { sb[k * kShadeBlock] = v; }
+    __device__ __forceinline__ float Ru(int k) const { return sb[(kNLambda + k) * kShadeBlock]; }
+    __device__ __forceinline__ void SetRu(int k, float v) { sb[(kNLambda + k) * kShadeBlock] = v; }
+    __device__ __forceinline__ float Rl(int k) const { return sb[(2 * kNLambda + k) * kShadeBlock]; }
+    __device__ __forceinline__ void SetRl(int k, float v) { sb[(2 * kNLambda + k) * kShadeBlock] = v; }
+    __device__ __forceinline__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
+    __device__ __forceinline__ void ShadowBegin() { slot = QueuePush(nShadow); }
+    __device__ __forceinline__ void SetLd(int k, float v) { pb.Ld[(long long)k * pb.n + slot] = v; }
+    __device__ void ShadowEndVol(bool valid, V3 o, V3 d, float tMax, const ShadowVolInfo &info) {
+        DevIO tmp(pb, path, nShadow, nullptr);
+        tmp.slot = slot;
+        tmp.ShadowEndVol(valid, o, d, tMax, info);
+    }
+};
+
 // ---- camera rays: RayIntegrator::EvaluatePixelSample up to GenerateRay (cpu/integrators.cpp:228-262)
 __global__ void __launch_bounds__(kShadeBlock)
 GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nActive, int firstSample,
@@ -305,18 +331,47 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
 // ---- volpath: the rays of this iteration that travel in a medium (cpu/integrators.cpp:968-1075).  Absorbed and
 // scattered paths are finished here (their hit slot is marked consumed); survivors go on to classify / shade
 // with beta, r_u, r_l rescaled.
-template <int LBVH>
-__global__ void __launch_bounds__(kShadeBlock)
-VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width) {
+// Work lists by kind of medium, so that a warp walks one kind (a homogeneous medium is one segment and a few
+// collisions, a density grid a DDA with many): mode 0 = the iteration's rays -> matQ[0] (homogeneous) / matQ[1]
+// (grid), lengths in counts[6] / counts[7]; mode 1 = the live light-sample rays -> matQ[0] (no medium) / matQ[1]
+// (homogeneous) / matQ[2] (grid), lengths in counts[2..4] (the material queues of this iteration are spent by then).
+__global__ void __launch_bounds__(256)
+VolSortKernel(RenderSceneDev rs, PassBuffers pb, int depth, int mode) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     int *counts = pb.counts + kCountStride * depth;
-    if (t >= counts[0]) return;
+    const long long n = pb.n;
+    if (mode == 0) {
+        if (t >= counts[0]) return;
+        if (pb.rays[depth & 1][7ll * t + 6] < 0) return;  // a sample without a camera ray
+        int medium = pb.ints[4 * n + pb.rayPath[depth & 1][t]];
+        if (medium < 0) return;
+        int kind = rs.media[medium].type == 0 ? 0 : 1;
+        for (int k = 0; k < 2; ++k)
+            if (kind == k) pb.matQ[k][QueuePush(counts + 6 + k)] = t;
+    } else {
+        if (t >= counts[1]) return;
+        if (pb.shPath[t] < 0) return;
+        int medium = (int)pb.shAux[(long long)kShadowAuxWords * t + 2];
+        int kind = medium < 0 ? 0 : (rs.media[medium].type == 0 ? 1 : 2);
+        for (int k = 0; k < 3; ++k)
+            if (kind == k) pb.matQ[k][QueuePush(counts + 2 + k)] = t;
+    }
+}
+
+#ifndef B2_VOL_MIN_BLOCKS
+#define B2_VOL_MIN_BLOCKS 3
+#endif
+template <int LBVH>
+__global__ void __launch_bounds__(kShadeBlock, B2_VOL_MIN_BLOCKS)
+VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width, int kind) {
+    int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    int *counts = pb.counts + kCountStride * depth;
+    if (qi >= counts[6 + kind]) return;
+    const int t = pb.matQ[kind][qi];
     const int cur = depth & 1, nxt = cur ^ 1;
     const long long n = pb.n;
     int path = pb.rayPath[cur][t];
-    if (pb.ints[4 * n + path] < 0) return;  // not in a medium
     const float *r = pb.rays[cur] + 7ll * t;
-    if (r[6] < 0) return;  // a sample without a camera ray
     PathRegs p;
     LoadHeader(pb, path, p);
     int pix = path % nPixels;
@@ -327,8 +382,24 @@ VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int w
     p.rayTMax = r[6];
     uint32_t slot = pb.hits[6ll * t];
     float tHit = slot == kMissTag ? INFINITY : __uint_as_float(pb.hits[6ll * t + 1]);
-    GlobalIO io(pb, path, counts + 1);
-    int res = VolMediumStep<GlobalIO, LBVH>(rs, p, tHit, io);
+    __shared__ float sstate[3 * kNLambda * kShadeBlock];
+    float *mine = sstate + threadIdx.x;
+#pragma unroll 8
+    for (int k = 0; k < kNLambda; ++k) {
+        mine[k * kShadeBlock] = pb.beta[k * n + path];
+        mine[(kNLambda + k) * kShadeBlock] = pb.ru[k * n + path];
+        mine[(2 * kNLambda + k) * kShadeBlock] = pb.rl[k * n + path];
+    }
+    MediumIO io(pb, path, counts + 1, mine);
+    int res = VolMediumStep<MediumIO, LBVH>(rs, p, tHit, io);
+    if (res != VOL_TERMINATED) {
+#pragma unroll 8
+        for (int k = 0; k < kNLambda; ++k) {
+            pb.beta[k * n + path] = mine[k * kShadeBlock];
+            pb.ru[k * n + path] = mine[(kNLambda + k) * kShadeBlock];
+            pb.rl[k * n + path] = mine[(2 * kNLambda + k) * kShadeBlock];
+        }
+    }
     if (res == VOL_SURVIVE) {
         StoreHeader(pb, path, p);
         return;
@@ -348,12 +419,12 @@ VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int w
 // ---- volpath: one segment of every light sample's transmittance walk (cpu/integrators.cpp:1334-1395).  pb.shHits
 // holds the closest hits of the shadow rays.  A walk that reaches the light adds its estimate to the path's
 // radiance; one that meets an interface leaves its next ray in the same slot and counts in pb.shContinue.
-__global__ void __launch_bounds__(kShadeBlock)
-ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
-    int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= pb.counts[kCountStride * depth + 1]) return;
+__global__ void __launch_bounds__(kShadeBlock, B2_VOL_MIN_BLOCKS)
+ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth, int kind) {
+    int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= pb.counts[kCountStride * depth + 2 + kind]) return;
+    const int t = pb.matQ[kind][qi];
     int path = pb.shPath[t];
-    if (path < 0) return;
     const long long n = pb.n;
     float *ray = pb.shRays + 7ll * t;
     uint32_t *a = pb.shAux + (long long)kShadowAuxWords * t;
@@ -542,14 +613,22 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
 cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width, int nActive,
                             cudaStream_t stream) {
     int grid = Blocks(nActive, kShadeBlock);
-    if (rs.integrator.lightSampler == 2)
-        VolMediumKernel<1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
-    else
-        VolMediumKernel<0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);
+    VolSortKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth, 0);
+    for (int kind = 0; kind < 2; ++kind) {
+        if (rs.integrator.lightSampler == 2)
+            VolMediumKernel<1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+        else
+            VolMediumKernel<0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+    }
     return cudaGetLastError();
 }
 cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {
-    ShadowTrKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth);
+    // counts[2..4] of this iteration: the material queues are spent, the slots hold the walk queues' lengths
+    cudaError_t e = cudaMemsetAsync(pb.counts + kCountStride * depth + 2, 0, 3 * sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    VolSortKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth, 1);
+    for (int kind = 0; kind < 3; ++kind)
+        ShadowTrKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
     return cudaGetLastError();
 }
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {

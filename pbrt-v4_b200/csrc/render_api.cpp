@@ -219,7 +219,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                 ++launches;
                 if (r->dev.nMedia) {
                     B2_CUDA(ctx, LaunchVolMedium(r->dev, pb, j, nPix, width, nActive, ctx->stream));
-                    ++launches;
+                    launches += 3;
                 }
                 B2_CUDA(ctx, LaunchClassify(r->dev, pb, j, nActive, ctx->stream));
                 ++launches;
@@ -237,7 +237,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                                                        r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
                                                        ctx->nodeMin, ctx->stream, true, nShadow));
                     B2_CUDA(ctx, LaunchShadowTr(r->dev, pb, j, hc[0], ctx->stream));
-                    launches += 2;
+                    launches += 5;
                     B2_CUDA(ctx, cudaMemcpyAsync(&live, pb.shContinue, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
                     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
                 }

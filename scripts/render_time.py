@@ -13,6 +13,9 @@ import pbrt_v4_b200 as P  # noqa: E402
 
 name = sys.argv[1] if len(sys.argv) > 1 else "cornell_r512_s64"
 rsc = P.RenderScene.load(os.path.join(ROOT, "tests", "golden", name + ".b2rs"))
+if name == "config5_full":  # the frame tables hold a small grid: swap the full-size one in (as bench.py does)
+    g = int(os.environ.get("B200PT_C5_GRID", "256"))
+    rsc = P.RenderScene(P.scenes.with_density_grid(rsc.d, P.scenes.procedural_density(g)))
 res, spp = rsc.resolution[0], rsc.spp
 nsamp = int(sys.argv[2]) if len(sys.argv) > 2 else spp
 r = P.B200Renderer(rsc)
