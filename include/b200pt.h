@@ -60,10 +60,16 @@ typedef struct b200pt_scene b200pt_scene;
 typedef struct b200pt_mesh {
     int32_t object;
     uint32_t n_vertices;
-    uint32_t n_triangles;
+    uint32_t n_triangles;   /* number of primitives: triangles, or patches for a bilinear mesh */
     const float *p;         /* 3 * n_vertices */
-    const int32_t *indices; /* 3 * n_triangles */
+    const int32_t *indices; /* 3 per triangle; 4 per bilinear patch: p00 p10 p01 p11 */
+    /* 0 = triangle mesh; 1 = bilinear patch mesh (BilinearPatchMesh, util/mesh.h:47-77; BilinearPatch::Intersect
+     * / IntersectP, shapes.cpp:1131-1156 over IntersectBilinearPatch, shapes.h:1279-1347).  Hits on a patch report
+     * prim = the patch index and (b1, b2) = the patch's (u, v).  The traversal entry points take both kinds; the
+     * render path (b200pt_render_create) takes triangle meshes only so far. */
+    uint32_t kind;
 } b200pt_mesh;
+enum { B200PT_MESH_TRIANGLES = 0, B200PT_MESH_BILINEAR = 1 };
 
 /* One object instance (TransformedPrimitive, cpu/primitive.cpp:112-131).
  * instanceId reported in hits = 1 + index in instances[] (scene.cpp:1560-1573). */
@@ -77,7 +83,7 @@ typedef struct b200pt_instance {
  * (LinearBVHNode, cpu/aggregates.cpp:129-137: 32 B = bounds 24 B, i32
  * primitivesOffset | secondChildOffset, u16 nPrimitives, u8 axis, pad).
  * prims: 3 u32 per ordered primitive {kind, a, b}: kind 0 = triangle
- * (a = mesh, b = tri); kind 1 = instance (a = instanceId, 1-based). */
+ * (a = mesh, b = tri); kind 1 = instance (a = instanceId, 1-based); kind 2 = bilinear patch (a = mesh, b = patch). */
 typedef struct b200pt_bvh2 {
     int32_t object; /* -1 = top level */
     uint32_t n_nodes;

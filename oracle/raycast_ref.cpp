@@ -19,8 +19,10 @@
 //   closest   <rays.f32> <hits.bin> [nthreads] [reps]
 //   any       <rays.f32> <occl.u8>  [nthreads] [reps]
 // Scene file (little endian), written by pbrt-v4_b200/scenes.py:
-//   u32 magic 'B2SC', u32 version=1, u32 nMeshes, u32 nInstances
-//   per mesh: i32 object (-1 = world), u32 nVerts, u32 nTris, f32 P[3*nVerts], i32 idx[3*nTris]
+//   u32 magic 'B2SC', u32 version=2, u32 nMeshes, u32 nInstances
+//   per mesh: i32 object (-1 = world), u32 nVerts, u32 nPrims, u32 kind (0 triangles, 1 bilinear patches),
+//             f32 P[3*nVerts], i32 idx[(3 or 4)*nPrims]
+//   (a bilinear mesh becomes a BilinearPatchMesh + BilinearPatch::CreatePatches, util/mesh.h:47-77, shapes.cpp:1005)
 //   per instance: u32 object, f32 renderFromInstance[16], f32 instanceFromRender[16] (row major)
 // Rays: n x 7 f32 (o.xyz, d.xyz, tMax).  Hits: n x 12 words
 //   {u32 mesh, u32 tri, u32 instanceId, f32 t, f32 u, f32 v, f32 p[3], f32 n[3]}, miss: mesh = 0xFFFFFFFF.
@@ -100,7 +102,7 @@ static Scene loadScene(const char *fn) {
     if (!f)
         die("cannot open scene");
     uint32_t hdr[4];
-    if (fread(hdr, 4, 4, f) != 4 || hdr[0] != 0x43533242u || hdr[1] != 1)
+    if (fread(hdr, 4, 4, f) != 4 || hdr[0] != 0x43533242u || hdr[1] != 2)
         die("bad scene header");
     uint32_t nMeshes = hdr[2], nInst = hdr[3];
     g_matBase = (char *)aligned_alloc(64, 64 * size_t(nMeshes + 2));
@@ -110,24 +112,30 @@ static Scene loadScene(const char *fn) {
     static Transform identity;
     for (uint32_t m = 0; m < nMeshes; ++m) {
         int32_t object;
-        uint32_t nv, nt;
-        if (fread(&object, 4, 1, f) != 1 || fread(&nv, 4, 1, f) != 1 || fread(&nt, 4, 1, f) != 1)
+        uint32_t nv, nt, kind;
+        if (fread(&object, 4, 1, f) != 1 || fread(&nv, 4, 1, f) != 1 || fread(&nt, 4, 1, f) != 1 ||
+            fread(&kind, 4, 1, f) != 1)
             die("short read");
         std::vector<float> P = readVec<float>(f, 3 * size_t(nv));
-        std::vector<int> idx = readVec<int>(f, 3 * size_t(nt));
+        std::vector<int> idx = readVec<int>(f, (kind == 1 ? 4 : 3) * size_t(nt));
         std::vector<Point3f> p(nv);
         for (uint32_t i = 0; i < nv; ++i)
             p[i] = Point3f(P[3 * i], P[3 * i + 1], P[3 * i + 2]);
         std::vector<int> face(nt);
         for (uint32_t i = 0; i < nt; ++i)
             face[i] = int(i);  // faceIndex := triIndex, read back from the hit
+        std::vector<Primitive> &dst = object < 0 ? world : objPrims[object];
+        if (kind == 1) {
+            BilinearPatchMesh *bm = alloc.new_object<BilinearPatchMesh>(
+                identity, false, std::move(idx), std::move(p), std::vector<Normal3f>(), std::vector<Point2f>(),
+                std::move(face), nullptr, alloc);
+            for (Shape s : BilinearPatch::CreatePatches(bm, alloc)) dst.push_back(new SimplePrimitive(s, meshMaterial(m)));
+            continue;
+        }
         TriangleMesh *mesh = alloc.new_object<TriangleMesh>(
             identity, false, std::move(idx), std::move(p), std::vector<Vector3f>(),
             std::vector<Normal3f>(), std::vector<Point2f>(), std::move(face), alloc);
         pstd::vector<Shape> tris = Triangle::CreateTriangles(mesh, alloc);
-        if (tris.size() && tris[0].Cast<Triangle>()->meshIndex != int(m))
-            die("mesh index mismatch");
-        std::vector<Primitive> &dst = object < 0 ? world : objPrims[object];
         for (Shape s : tris)
             dst.push_back(new SimplePrimitive(s, meshMaterial(m)));
     }
@@ -199,9 +207,14 @@ static void dumpBVH(const Scene &sc, const char *out) {
         for (const Primitive &p : bvh->primitives) {
             uint32_t rec[3] = {0, 0, 0};
             if (const SimplePrimitive *sp = p.CastOrNullptr<SimplePrimitive>()) {
-                const Triangle *t = sp->shape.Cast<Triangle>();
-                rec[1] = t->meshIndex;
-                rec[2] = t->triIndex;
+                // the mesh id of the scene file is carried by the per-mesh material (triangle and bilinear
+                // meshes have separate index spaces inside the reference)
+                rec[1] = meshOfMaterial(sp->material);
+                if (const BilinearPatch *bp = sp->shape.CastOrNullptr<BilinearPatch>()) {
+                    rec[0] = 2;
+                    rec[2] = bp->blpIndex;
+                } else
+                    rec[2] = sp->shape.Cast<Triangle>()->triIndex;
             } else if (const TransformedPrimitive *tp = p.CastOrNullptr<TransformedPrimitive>()) {
                 rec[0] = 1;
                 rec[1] = tp->instanceId;

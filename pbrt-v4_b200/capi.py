@@ -22,7 +22,7 @@ assert HIT_DTYPE.itemsize == 24 and NODE32_DTYPE.itemsize == 32
 
 class Mesh(C.Structure):
     _fields_ = [("object", C.c_int32), ("n_vertices", C.c_uint32), ("n_triangles", C.c_uint32),
-                ("p", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_int32))]
+                ("p", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_int32)), ("kind", C.c_uint32)]
 
 
 class Instance(C.Structure):

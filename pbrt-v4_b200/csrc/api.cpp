@@ -161,6 +161,7 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     s->dev.nPrims = uint32_t(h.prims.size());
     s->dev.nInstances = uint32_t(h.instances.size());
     s->dev.maxDepth = h.maxDepth;
+    s->dev.hasPatches = h.hasPatches ? 1u : 0u;
     s->stats.n_triangles = h.nTriangles;
     s->stats.n_instances = h.instances.size();
     s->stats.n_bvh2_nodes = h.nodes.size();

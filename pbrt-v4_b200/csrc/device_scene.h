@@ -10,6 +10,7 @@ namespace b200pt {
 //   triangle: p0,p1,p2 pre-gathered (the reference does vertexIndices -> p[] per
 //             test, shapes.cpp:326-328), mesh/tri = Triangle{meshIndex,triIndex}.
 //   instance: mesh == kInstanceTag, tri = index into DeviceScene::instances.
+//   bilinear patch: kind == 1; p0, p1, p2, p3 = p00, p10, p01, p11 (shapes.cpp:1134-1137), tri = patch index.
 struct alignas(32) PrimSlot {
     float p0[3];
     float p1[3];
@@ -17,7 +18,8 @@ struct alignas(32) PrimSlot {
     uint32_t mesh;
     uint32_t tri;
     uint32_t flags;
-    uint32_t pad[4];
+    float p3[3];
+    uint32_t kind;  // 0 triangle (or instance), 1 bilinear patch
 };
 static_assert(sizeof(PrimSlot) == 64, "PrimSlot is one 32-byte and one 16-byte load");
 constexpr uint32_t kInstanceTag = 0xFFFFFFFEu;
@@ -65,6 +67,7 @@ struct DeviceScene {
     uint32_t nPrims;
     uint32_t nInstances;
     uint32_t maxDepth;   // deepest root-to-leaf path over all trees (stack entries needed)
+    uint32_t hasPatches; // some PrimSlot is a bilinear patch (the kernels then read the slots' last 16 bytes)
 };
 
 }  // namespace b200pt

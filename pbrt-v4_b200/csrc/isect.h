@@ -238,4 +238,122 @@ B2_HD bool TriHit(const RayCtx &r, float tMax, const float *p0, const float *p1,
     return true;
 }
 
+// ------------------------------------------------------------------ bilinear patches
+// IntersectBilinearPatch (shapes.h:1279-1347), operation for operation: Cross = DifferenceOfProducts per
+// component (util/vecmath.h:1001-1006), Dot = plain sum of products, Lerp(t, a, b) = (1 - t) * a + t * b,
+// Determinant(SquareMatrix<3>) (util/math.h:1420-1426), Quadratic (util/math.h:614-637).
+B2_HD void Cross3(const float *v, const float *w, float *o) {
+    o[0] = DiffOfProducts(v[1], w[2], v[2], w[1]);
+    o[1] = DiffOfProducts(v[2], w[0], v[0], w[2]);
+    o[2] = DiffOfProducts(v[0], w[1], v[1], w[0]);
+}
+B2_HD float Dot3(const float *a, const float *b) {
+    return B2_ADD(B2_ADD(B2_MUL(a[0], b[0]), B2_MUL(a[1], b[1])), B2_MUL(a[2], b[2]));
+}
+// rows (a0 b0 c0), (a1 b1 c1), (a2 b2 c2)
+B2_HD float Det3(const float *a, const float *b, const float *c) {
+    float minor12 = DiffOfProducts(b[1], c[2], c[1], b[2]);
+    float minor02 = DiffOfProducts(a[1], c[2], c[1], a[2]);
+    float minor01 = DiffOfProducts(a[1], b[2], b[1], a[2]);
+    return B2_FMA(c[0], minor01, DiffOfProducts(a[0], minor12, b[0], minor02));
+}
+B2_HD bool QuadraticRef(float a, float b, float c, float *t0, float *t1) {
+    if (a == 0) {
+        if (b == 0) return false;
+        *t0 = *t1 = B2_DIV(-c, b);
+        return true;
+    }
+    float discrim = DiffOfProducts(b, b, B2_MUL(4.f, a), c);
+    if (discrim < 0) return false;
+    float rootDiscrim = sqrtf(discrim);
+    float q = B2_MUL(-0.5f, B2_ADD(b, copysignf(rootDiscrim, b)));
+    *t0 = B2_DIV(q, a);
+    *t1 = B2_DIV(c, q);
+    if (*t0 > *t1) {
+        float t = *t0;
+        *t0 = *t1;
+        *t1 = t;
+    }
+    return true;
+}
+
+// One candidate root u of the patch quadratic: v and t numerators over p2 = |d x ud|^2
+B2_HD void BilinearCandidate(const float *o, const float *d, const float *p00, const float *p10, const float *p01,
+                             const float *p11, float u, float &vNum, float &tNum, float &p2) {
+    float uo[3], ud[3], deltao[3], perp[3];
+    const float om = B2_SUB(1.f, u);
+    for (int k = 0; k < 3; ++k) {
+        uo[k] = B2_ADD(B2_MUL(om, p00[k]), B2_MUL(u, p10[k]));
+        float e = B2_ADD(B2_MUL(om, p01[k]), B2_MUL(u, p11[k]));
+        ud[k] = B2_SUB(e, uo[k]);
+        deltao[k] = B2_SUB(uo[k], o[k]);
+    }
+    Cross3(d, ud, perp);
+    p2 = B2_ADD(B2_ADD(B2_MUL(perp[0], perp[0]), B2_MUL(perp[1], perp[1])), B2_MUL(perp[2], perp[2]));
+    // SquareMatrix<3>(deltao.x, d.x, perp.x, deltao.y, d.y, perp.y, deltao.z, d.z, perp.z): the matrix rows are
+    // (deltao[i], d[i], perp[i]); Det3 takes its three columns
+    vNum = Det3(deltao, d, perp);
+    tNum = Det3(deltao, ud, perp);
+}
+
+// Returns true and fills t, u, v on a hit with t < tMax.
+B2_HD bool BilinearHit(const RayCtx &r, float tMax, const float *p00, const float *p10, const float *p01,
+                       const float *p11, float &tOut, float &uOut, float &vOut) {
+    const float o[3] = {r.ox, r.oy, r.oz}, d[3] = {r.dx, r.dy, r.dz};
+    float e0[3], e1[3], cr[3];
+    for (int k = 0; k < 3; ++k) {
+        e0[k] = B2_SUB(p10[k], p00[k]);
+        e1[k] = B2_SUB(p01[k], p11[k]);
+    }
+    Cross3(e0, e1, cr);
+    float a = Dot3(cr, d);
+    for (int k = 0; k < 3; ++k) {
+        e0[k] = B2_SUB(p00[k], o[k]);
+        e1[k] = B2_SUB(p01[k], p00[k]);
+    }
+    Cross3(e0, d, cr);
+    float c = Dot3(cr, e1);
+    for (int k = 0; k < 3; ++k) {
+        e0[k] = B2_SUB(p10[k], o[k]);
+        e1[k] = B2_SUB(p11[k], p10[k]);
+    }
+    Cross3(e0, d, cr);
+    float b = B2_SUB(Dot3(cr, e1), B2_ADD(a, c));
+    float u1, u2;
+    if (!QuadraticRef(a, b, c, &u1, &u2)) return false;
+    // gamma(10) * (sum of the max |component| of o, d and the four vertices), added left to right
+    float eps = Max3Abs(o[0], o[1], o[2]);
+    eps = B2_ADD(eps, Max3Abs(d[0], d[1], d[2]));
+    eps = B2_ADD(eps, Max3Abs(p00[0], p00[1], p00[2]));
+    eps = B2_ADD(eps, Max3Abs(p10[0], p10[1], p10[2]));
+    eps = B2_ADD(eps, Max3Abs(p01[0], p01[1], p01[2]));
+    eps = B2_ADD(eps, Max3Abs(p11[0], p11[1], p11[2]));
+    eps = B2_MUL(GammaF(10), eps);
+    float t = tMax, u = 0, v = 0;
+    if (0 <= u1 && u1 <= 1) {
+        float v1, t1, p2;
+        BilinearCandidate(o, d, p00, p10, p01, p11, u1, v1, t1, p2);
+        if (t1 > B2_MUL(p2, eps) && 0 <= v1 && v1 <= p2) {
+            u = u1;
+            v = B2_DIV(v1, p2);
+            t = B2_DIV(t1, p2);
+        }
+    }
+    if (0 <= u2 && u2 <= 1 && u2 != u1) {
+        float v2, t2, p2;
+        BilinearCandidate(o, d, p00, p10, p01, p11, u2, v2, t2, p2);
+        t2 = B2_DIV(t2, p2);
+        if (0 <= v2 && v2 <= p2 && t > t2 && t2 > eps) {
+            t = t2;
+            u = u2;
+            v = B2_DIV(v2, p2);
+        }
+    }
+    if (t >= tMax) return false;
+    tOut = t;
+    uOut = u;
+    vOut = v;
+    return true;
+}
+
 }  // namespace b200pt

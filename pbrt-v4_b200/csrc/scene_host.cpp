@@ -21,6 +21,25 @@ inline Box TriBox(const float *p0, const float *p1, const float *p2) {
     return b;
 }
 
+// BilinearPatch::Bounds = Union(Bounds3f(p00, p01), Bounds3f(p10, p11)) (shapes.cpp:1073-1081)
+inline Box PatchBox(const float *p00, const float *p10, const float *p01, const float *p11) {
+    Box b;
+    for (int k = 0; k < 3; ++k) {
+        b.lo[k] = std::min(std::min(p00[k], p01[k]), std::min(p10[k], p11[k]));
+        b.hi[k] = std::max(std::max(p00[k], p01[k]), std::max(p10[k], p11[k]));
+    }
+    return b;
+}
+// box and BVH record of primitive i of a mesh of either kind
+inline Box MeshPrimBox(const b200pt_mesh &mesh, uint32_t i) {
+    if (mesh.kind == B200PT_MESH_BILINEAR) {
+        const int32_t *v = mesh.indices + 4ull * i;
+        return PatchBox(mesh.p + 3ull * v[0], mesh.p + 3ull * v[1], mesh.p + 3ull * v[2], mesh.p + 3ull * v[3]);
+    }
+    const int32_t *v = mesh.indices + 3ull * i;
+    return TriBox(mesh.p + 3ull * v[0], mesh.p + 3ull * v[1], mesh.p + 3ull * v[2]);
+}
+
 struct PrimRef {
     uint32_t kind, a, b;
 };
@@ -77,11 +96,17 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             err = "mesh with null arrays";
             return B200PT_ERR_INVALID;
         }
-        for (uint64_t i = 0; i < 3ull * mesh.n_triangles; ++i)
+        if (mesh.kind > B200PT_MESH_BILINEAR) {
+            err = "unknown mesh kind";
+            return B200PT_ERR_INVALID;
+        }
+        const uint64_t perPrim = mesh.kind == B200PT_MESH_BILINEAR ? 4 : 3;
+        for (uint64_t i = 0; i < perPrim * mesh.n_triangles; ++i)
             if (mesh.indices[i] < 0 || uint32_t(mesh.indices[i]) >= mesh.n_vertices) {
                 err = "vertex index out of range";
                 return B200PT_ERR_INVALID;
             }
+        if (mesh.kind == B200PT_MESH_BILINEAR && mesh.n_triangles) out.hasPatches = true;
         objMeshes[mesh.object < 0 ? -1 : mesh.object].push_back(m);
         nTri += mesh.n_triangles;
     }
@@ -143,9 +168,8 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             for (uint32_t m : kv.second) {
                 const b200pt_mesh &mesh = desc->meshes[m];
                 for (uint32_t i = 0; i < mesh.n_triangles; ++i) {
-                    const int32_t *v = mesh.indices + 3ull * i;
-                    ob.push_back(TriBox(mesh.p + 3ull * v[0], mesh.p + 3ull * v[1], mesh.p + 3ull * v[2]));
-                    orf.push_back({0, m, i});
+                    ob.push_back(MeshPrimBox(mesh, i));
+                    orf.push_back({mesh.kind == B200PT_MESH_BILINEAR ? 2u : 0u, m, i});
                 }
             }
             if (ob.empty()) {
@@ -172,9 +196,8 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
         for (uint32_t m : objMeshes[-1]) {
             const b200pt_mesh &mesh = desc->meshes[m];
             for (uint32_t i = 0; i < mesh.n_triangles; ++i) {
-                const int32_t *v = mesh.indices + 3ull * i;
-                boxes.push_back(TriBox(mesh.p + 3ull * v[0], mesh.p + 3ull * v[1], mesh.p + 3ull * v[2]));
-                refs.push_back({0, m, i});
+                boxes.push_back(MeshPrimBox(mesh, i));
+                refs.push_back({mesh.kind == B200PT_MESH_BILINEAR ? 2u : 0u, m, i});
             }
         }
         for (uint32_t i = 0; i < desc->n_instances; ++i) {
@@ -235,8 +258,24 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                     const uint32_t *pr = &t.prims[3ull * (uint32_t(nd.offset) + k)];
                     PrimSlot s;
                     std::memset(&s, 0, sizeof s);
-                    if (pr[0] == 0) {
-                        if (pr[1] >= desc->n_meshes || pr[2] >= desc->meshes[pr[1]].n_triangles) {
+                    if (pr[0] == 2) {
+                        if (pr[1] >= desc->n_meshes || desc->meshes[pr[1]].kind != B200PT_MESH_BILINEAR ||
+                            pr[2] >= desc->meshes[pr[1]].n_triangles) {
+                            err = "bvh primitive refers to a missing bilinear patch";
+                            return B200PT_ERR_INVALID;
+                        }
+                        const b200pt_mesh &mesh = desc->meshes[pr[1]];
+                        const int32_t *v = mesh.indices + 4ull * pr[2];
+                        std::memcpy(s.p0, mesh.p + 3ull * v[0], 12);
+                        std::memcpy(s.p1, mesh.p + 3ull * v[1], 12);
+                        std::memcpy(s.p2, mesh.p + 3ull * v[2], 12);
+                        std::memcpy(s.p3, mesh.p + 3ull * v[3], 12);
+                        s.mesh = pr[1];
+                        s.tri = pr[2];
+                        s.kind = 1;
+                    } else if (pr[0] == 0) {
+                        if (pr[1] >= desc->n_meshes || desc->meshes[pr[1]].kind != B200PT_MESH_TRIANGLES ||
+                            pr[2] >= desc->meshes[pr[1]].n_triangles) {
                             err = "bvh primitive refers to a missing triangle";
                             return B200PT_ERR_INVALID;
                         }

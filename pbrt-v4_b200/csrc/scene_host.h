@@ -31,7 +31,8 @@ struct HostScene {
     uint32_t rootNode = 0;
     uint32_t maxDepth = 1;           // deepest path over all trees, in nodes
     float bounds[6] = {0, 0, 0, 0, 0, 0};
-    uint64_t nTriangles = 0;
+    uint64_t nTriangles = 0;         // primitives of both kinds
+    bool hasPatches = false;
     uint32_t nMeshes = 0;
     double buildSeconds = 0;
 };

@@ -65,7 +65,15 @@ TraverseBVH2Kernel(DeviceScene sc, const float *__restrict__ rays, long long n,
                         float p0[3] = {a.x, a.y, a.z}, p1[3] = {a.w, b.x, b.y}, p2[3] = {b.z, b.w, c.x};
                         float t, b0, b1, b2;
                         if (COUNT) ++cPrims;
-                        if (TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2)) {
+                        bool primHit;
+                        if (sc.hasPatches) {
+                            float4 d4 = __ldg(prims + 4 * slot + 3);
+                            float p3[3] = {d4.x, d4.y, d4.z};
+                            primHit = __float_as_uint(d4.w) == 1u ? BilinearHit(r, tMax, p0, p1, p2, p3, t, b1, b2)
+                                                                  : TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
+                        } else
+                            primHit = TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
+                        if (primHit) {
                             if (ANY) {
                                 any = true;
                                 break;

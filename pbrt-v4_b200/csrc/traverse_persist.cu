@@ -62,7 +62,8 @@ constexpr int kLocalDepth = 72;
 // pops: the parent ray is set up again from the ray buffer and the leaf loop resumes.  The parent
 // goes on with tMax = the t found in the object, not shifted back by dt, as the reference does.
 constexpr int kReturn = int(0x80000000u);
-template <bool ANY, bool COUNT, bool INTERNAL, bool INST>
+// PATCH: some leaf slots are bilinear patches (kind word of the slot's last 16 bytes); hits report (u, v).
+template <bool ANY, bool COUNT, bool INTERNAL, bool INST, bool PATCH>
 __global__ void __launch_bounds__(kBlock)
 TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200pt_hit *__restrict__ hits,
                       unsigned char *__restrict__ occluded, int *__restrict__ rayCounter,
@@ -231,7 +232,18 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                       p2[3] = {a.v[6], a.v[7], b.x};
                 float t, b0, b1, b2;
                 if (COUNT) ++cPrims;
-                if (TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2)) {
+                bool primHit;
+                if (PATCH) {
+                    float4 c4 = __ldg(reinterpret_cast<const float4 *>(prims + 64ll * slot + 48));
+                    if (__float_as_uint(c4.w) == 1u) {  // p0..p3 = p00, p10, p01, p11
+                        float p3[3] = {c4.x, c4.y, c4.z};
+                        b0 = 0.f;
+                        primHit = BilinearHit(r, tMax, p0, p1, p2, p3, t, b1, b2);
+                    } else
+                        primHit = TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
+                } else
+                    primHit = TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
+                if (primHit) {
                     if (ANY) {
                         anyHit = true;
                         break;
@@ -320,24 +332,17 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
                                                   nodeMin, nDev);
         return cudaGetLastError();
     };
-    if (sc.nInstances) {
-        if (any)
-            return counters ? pick(TraversePersistKernel<true, true, false, true>)
-                            : pick(TraversePersistKernel<true, false, false, true>);
-        if (internalHits)
-            return counters ? pick(TraversePersistKernel<false, true, true, true>)
-                            : pick(TraversePersistKernel<false, false, true, true>);
-        return counters ? pick(TraversePersistKernel<false, true, false, true>)
-                        : pick(TraversePersistKernel<false, false, false, true>);
-    }
-    if (any)
-        return counters ? pick(TraversePersistKernel<true, true, false, false>)
-                        : pick(TraversePersistKernel<true, false, false, false>);
-    if (internalHits)
-        return counters ? pick(TraversePersistKernel<false, true, true, false>)
-                        : pick(TraversePersistKernel<false, false, true, false>);
-    return counters ? pick(TraversePersistKernel<false, true, false, false>)
-                    : pick(TraversePersistKernel<false, false, false, false>);
+#define B2_PICK(ANYV, INTV, INSTV, PATCHV)                                                        \
+    (counters ? pick(TraversePersistKernel<ANYV, true, INTV, INSTV, PATCHV>)                      \
+              : pick(TraversePersistKernel<ANYV, false, INTV, INSTV, PATCHV>))
+#define B2_PICK_SCENE(ANYV, INTV)                                                                 \
+    (sc.nInstances ? (sc.hasPatches ? B2_PICK(ANYV, INTV, true, true) : B2_PICK(ANYV, INTV, true, false)) \
+                   : (sc.hasPatches ? B2_PICK(ANYV, INTV, false, true) : B2_PICK(ANYV, INTV, false, false)))
+    if (any) return B2_PICK_SCENE(true, false);
+    if (internalHits) return B2_PICK_SCENE(false, true);
+    return B2_PICK_SCENE(false, false);
+#undef B2_PICK_SCENE
+#undef B2_PICK
 }
 
 }  // namespace b200pt

@@ -150,7 +150,7 @@ def scene_desc(geometry, bvh, keep):
         p, idx = np.ascontiguousarray(m.p, np.float32), np.ascontiguousarray(m.indices, np.int32)
         keep += [p, idx]
         meshes[k] = capi.Mesh(int(m.object), p.shape[0], idx.shape[0], capi.fptr(p),
-                              idx.ctypes.data_as(C.POINTER(C.c_int32)))
+                              idx.ctypes.data_as(C.POINTER(C.c_int32)), int(getattr(m, "kind", 0)))
     barr = (capi.BVH2 * max(1, len(bvh) if bvh else 1))()
     nb = 0
     if bvh:

@@ -3,8 +3,9 @@ the little-endian scene file (`.b2sc`) that carries the same geometry to both
 the product (through capi / B200Aggregate) and the reference driver
 (oracle/raycast_ref.cpp).  numpy only; nothing here computes intersections.
 
-File layout:  u32 magic 'B2SC', u32 version=1, u32 nMeshes, u32 nInstances
-  per mesh:     i32 object (-1 world), u32 nVerts, u32 nTris, f32 P[3nV], i32 idx[3nT]
+File layout:  u32 magic 'B2SC', u32 version=2, u32 nMeshes, u32 nInstances
+  per mesh:     i32 object (-1 world), u32 nVerts, u32 nPrims, u32 kind (0 triangles, 1 bilinear patches),
+                f32 P[3nV], i32 idx[(3 or 4) nPrims]
   per instance: u32 object, f32 renderFromInstance[16], f32 instanceFromRender[16]
 """
 from dataclasses import dataclass, field
@@ -20,12 +21,13 @@ MAGIC = 0x43533242
 @dataclass
 class Mesh:
     p: np.ndarray            # (nv, 3) float32, render space
-    indices: np.ndarray      # (nt, 3) int32
+    indices: np.ndarray      # (nt, 3) int32; bilinear patches: (np, 4) = p00 p10 p01 p11
     object: int = -1         # -1: world; >= 0: object definition id
+    kind: int = 0            # 0 triangles, 1 bilinear patches
 
     def __post_init__(self):
         self.p = np.ascontiguousarray(self.p, dtype=np.float32).reshape(-1, 3)
-        self.indices = np.ascontiguousarray(self.indices, dtype=np.int32).reshape(-1, 3)
+        self.indices = np.ascontiguousarray(self.indices, dtype=np.int32).reshape(-1, 4 if self.kind == 1 else 3)
 
 
 @dataclass
@@ -50,10 +52,10 @@ class Scene:
 
     def write(self, path):
         with open(path, "wb") as f:
-            np.array([MAGIC, 1, len(self.meshes), len(self.instances)], dtype="<u4").tofile(f)
+            np.array([MAGIC, 2, len(self.meshes), len(self.instances)], dtype="<u4").tofile(f)
             for m in self.meshes:
                 np.array([m.object], dtype="<i4").tofile(f)
-                np.array([m.p.shape[0], m.indices.shape[0]], dtype="<u4").tofile(f)
+                np.array([m.p.shape[0], m.indices.shape[0], m.kind], dtype="<u4").tofile(f)
                 m.p.astype("<f4").tofile(f)
                 m.indices.astype("<i4").tofile(f)
             for i in self.instances:
@@ -134,6 +136,32 @@ def flattened(scene):
             if m.object == inst.object:
                 out.append(Mesh((m.p.astype(np.float64) @ M[:3, :3].T + M[:3, 3]).astype(np.float32), m.indices))
     return Scene(out)
+
+
+def patch_scene(n_patches=20000, n_tris=10000, seed=91, s=0.03):
+    """Bilinear patches (BilinearPatchMesh: 4 indices per patch, p00 p10 p01 p11) in the unit cube, one mesh of
+    twisted (non-planar) patches, one of planar parallelograms (the quadratic's a = 0 branch) and axis-aligned
+    squares, next to a triangle mesh, so leaves mix both kinds."""
+    rng = np.random.default_rng(seed)
+    def quads(n, twist, axis_aligned=False):
+        c = rng.uniform(0.05, 0.95, (n, 3))
+        e0 = rng.uniform(-s, s, (n, 3))
+        e1 = rng.uniform(-s, s, (n, 3))
+        if axis_aligned:
+            ax = rng.integers(0, 3, n)
+            e0[:] = 0
+            e1[:] = 0
+            e0[np.arange(n), (ax + 1) % 3] = s
+            e1[np.arange(n), (ax + 2) % 3] = s
+        p = np.stack([c, c + e0, c + e1, c + e0 + e1], axis=1)
+        p[:, 3] += twist * rng.uniform(-s, s, (n, 3))
+        return Mesh(p.reshape(-1, 3), np.arange(4 * n).reshape(n, 4), kind=1)
+    n1 = n_patches // 2
+    n2 = (n_patches - n1) // 2
+    meshes = [quads(n1, 1.0), quads(n2, 0.0), quads(n_patches - n1 - n2, 0.0, axis_aligned=True)]
+    if n_tris:
+        meshes.append(random_soup(n_tris, seed=seed + 1, s=s).meshes[0])
+    return Scene(meshes)
 
 
 def _quad(p0, p1, p2, p3):
@@ -233,7 +261,8 @@ def adversarial_rays(scene, n, seed=3):
     lying exactly in bounding planes."""
     rng = np.random.default_rng(seed)
     verts = np.concatenate([m.p[m.indices].reshape(-1, 3) for m in scene.meshes if m.object < 0], axis=0)
-    tris = np.concatenate([m.p[m.indices] for m in scene.meshes if m.object < 0], axis=0)
+    # (a bilinear patch contributes its first three corners: edges p00-p10, p10-p01 (a diagonal), p01-p00)
+    tris = np.concatenate([m.p[m.indices[:, :3]] for m in scene.meshes if m.object < 0], axis=0)
     k = n // 4
     rays = np.empty((4 * k, 7), dtype=np.float32)
     # 1) through vertices from random outside origins

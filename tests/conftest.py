@@ -45,19 +45,27 @@ def hostcheck_bin():
     return out
 
 
-def hit_mismatches(mine, ref):
+def hit_mismatches(mine, ref, scene=None):
     """Bit-exact comparison of product hits (capi.HIT_DTYPE) with reference hits
     (refrun.REF_HIT_DTYPE).  ids and t by bits; barycentrics through the reference's uv
     (default uv (0,0),(1,0),(1,1): u = b1 + b2, v = b2; `+ 0.0` folds -0, which the
-    reference's b0*0 + ... sum also does, shapes.h:884-1010)."""
+    reference's b0*0 + ... sum also does, shapes.h:884-1010).  Hits on bilinear patches (meshes of
+    `scene` with kind 1) carry the patch's own (u, v), compared as they are (shapes.h:1396-1472)."""
     hit = ref["mesh"] != 0xFFFFFFFF
     z = np.float32(0.0)
     bad = mine["mesh"] != ref["mesh"]
     bad |= hit & (mine["prim"] != ref["prim"])
     bad |= hit & (mine["instance"] != ref["instance"])
     bad |= hit & (mine["t"].view("u4") != ref["t"].view("u4"))
-    bad |= hit & ((mine["b2"] + z).view("u4") != (ref["uv"][:, 1] + z).view("u4"))
-    bad |= hit & (((mine["b1"] + mine["b2"]).astype("f4") + z).view("u4") != (ref["uv"][:, 0] + z).view("u4"))
+    patch = np.zeros(len(ref), bool)
+    if scene is not None:
+        kinds = np.array([getattr(m, "kind", 0) for m in scene.meshes] + [0], np.int64)
+        patch = hit & (kinds[np.minimum(ref["mesh"], len(kinds) - 1)] == 1)
+    tri = hit & ~patch
+    bad |= tri & ((mine["b2"] + z).view("u4") != (ref["uv"][:, 1] + z).view("u4"))
+    bad |= tri & (((mine["b1"] + mine["b2"]).astype("f4") + z).view("u4") != (ref["uv"][:, 0] + z).view("u4"))
+    bad |= patch & (mine["b1"].view("u4") != ref["uv"][:, 0].view("u4"))
+    bad |= patch & (mine["b2"].view("u4") != ref["uv"][:, 1].view("u4"))
     return bad
 
 

@@ -19,7 +19,10 @@ def cases(S):
     cb = S.cornell_box()
     sheet = S.Scene([S.grid_sheet(32, 32, jitter=0.0), S.grid_sheet(24, 24, z=0.75, jitter=0.02, seed=9)])
     inst = S.instanced_scene(n_objects=3, tris_per_object=600, n_instances=24, world_tris=1500, seed=41)
+    patches = S.patch_scene(6000, 3000, seed=95)
     return {
+        "patches_primary": (patches, S.primary_rays(30000, seed=38)),
+        "patches_adversarial": (patches, S.adversarial_rays(patches, 20000, seed=39)),
         "instanced_primary": (inst, S.primary_rays(30000, seed=36)),
         "instanced_adversarial": (inst, S.adversarial_rays(S.flattened(inst), 20000, seed=37)),
         "soup20k_primary": (soup, S.primary_rays(40000, seed=31)),
@@ -168,18 +171,24 @@ if __name__ == "__main__":
     import pbrt_v4_b200 as P
     import refrun
     out = os.path.dirname(os.path.abspath(__file__))
-    if "--config5-only" in sys.argv:
+    if any(a.startswith("--only=") for a in sys.argv):
+        pass
+    elif "--config5-only" in sys.argv:
         make_config5_goldens(P, refrun, out)
         sys.exit(0)
     if "--config4-only" in sys.argv:
         make_config4_goldens(P, refrun, out)
         sys.exit(0)
-    make_render_goldens(P, refrun, out)
-    make_config4_goldens(P, refrun, out)
-    make_config5_goldens(P, refrun, out)
+    if not any(a.startswith("--only=") for a in sys.argv):
+        make_render_goldens(P, refrun, out)
+        make_config4_goldens(P, refrun, out)
+        make_config5_goldens(P, refrun, out)
     if "--render-only" in sys.argv:
         sys.exit(0)
+    only = [a.split("=", 1)[1].split(",") for a in sys.argv if a.startswith("--only=")]
     for name, (sc, rays) in cases(P.scenes).items():
+        if only and name not in only[0]:
+            continue
         rs = refrun.RefScene(sc)
         hits, _ = rs.closest(rays)
         occ, _ = rs.any(rays)

@@ -23,7 +23,7 @@ def test_header_symbols_exported(P):
 
 def test_version_and_struct_sizes(P):
     assert P.capi.lib().b200pt_version() == 100
-    assert ctypes.sizeof(P.capi.Mesh) == 32
+    assert ctypes.sizeof(P.capi.Mesh) == 40  # + kind, padded to the pointers
     assert ctypes.sizeof(P.capi.Instance) == 4 + 128
     assert ctypes.sizeof(P.capi.SceneDesc) == 56
     assert P.capi.HIT_DTYPE.itemsize == 24

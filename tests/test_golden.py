@@ -14,7 +14,7 @@ _spec = importlib.util.spec_from_file_location("make_golden", os.path.join(ROOT,
 G = importlib.util.module_from_spec(_spec)
 _spec.loader.exec_module(G)
 NAMES = ["soup20k_primary", "soup20k_adversarial", "cornell_camera", "cornell_adversarial", "sheets_adversarial",
-         "instanced_primary", "instanced_adversarial"]
+         "instanced_primary", "instanced_adversarial", "patches_primary", "patches_adversarial"]
 
 
 @pytest.mark.parametrize("name", NAMES)
@@ -38,9 +38,9 @@ def test_host_arithmetic_matches_fixture(P, hostcheck_bin, name, tmp_path):
         path = os.path.join(str(tmp_path), "scene.b2sc")
     sc.write(RS.path)
     mine, occ = run_hostcheck(hostcheck_bin, P, RS, rays)
-    assert hit_mismatches(mine, gold["hits"]).sum() == 0
+    assert hit_mismatches(mine, gold["hits"], sc).sum() == 0
     assert np.array_equal(occ, gold["occ"])
     sh = P.scenes.shadow_rays(rays, gold["hits"], seed=35)
     mine, occ = run_hostcheck(hostcheck_bin, P, RS, sh)
-    assert hit_mismatches(mine, gold["shadow_hits"]).sum() == 0
+    assert hit_mismatches(mine, gold["shadow_hits"], sc).sum() == 0
     assert np.array_equal(occ, gold["shadow_occ"])

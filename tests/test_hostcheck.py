@@ -32,6 +32,9 @@ CASES = {
     # object instances (TransformedPrimitive, cpu/primitive.cpp:112-131): interval ray transform, t not shifted back
     "instanced_primary": lambda S: (S.instanced_scene(), "primary"),
     "instanced_adversarial": lambda S: (S.instanced_scene(seed=78), "adversarial"),
+    # bilinear patches (IntersectBilinearPatch, shapes.h:1279-1347) mixed with triangles: (u, v) and t bit-exact
+    "patches_primary": lambda S: (S.patch_scene(), "primary"),
+    "patches_adversarial": lambda S: (S.patch_scene(8000, 4000, seed=93), "adversarial"),
     "instanced_only": lambda S: (S.instanced_scene(n_instances=12, world_tris=0, seed=79), "adversarial"),
 }
 
@@ -54,12 +57,15 @@ def test_host_arithmetic_bit_exact(P, refrun, hostcheck_bin, case, layout):
     assert (ref["mesh"] != 0xFFFFFFFF).mean() > 0.3
     if sc.instances:
         assert (ref["instance"] != 0).mean() > 0.2
-    assert hit_mismatches(mine, ref).sum() == 0
+    if any(m.kind == 1 for m in sc.meshes):
+        kinds = np.array([m.kind for m in sc.meshes] + [0])
+        assert (kinds[np.minimum(ref["mesh"], len(sc.meshes))] == 1).mean() > 0.2  # patches are hit
+    assert hit_mismatches(mine, ref, sc).sum() == 0
     assert (occ != occ_ref).sum() == 0
     # shadow rays from the hit points (unnormalised d, tMax = 1 - 1e-4)
     sh = S.shadow_rays(rays, mine)
     ref2, _ = rs.closest(sh)
     occ_ref2, _ = rs.any(sh)
     mine2, occ2 = run_hostcheck(hostcheck_bin, P, rs, sh, layout)
-    assert hit_mismatches(mine2, ref2).sum() == 0
+    assert hit_mismatches(mine2, ref2, sc).sum() == 0
     assert (occ2 != occ_ref2).sum() == 0

@@ -16,7 +16,7 @@ _spec = importlib.util.spec_from_file_location("make_golden", os.path.join(ROOT,
 G = importlib.util.module_from_spec(_spec)
 _spec.loader.exec_module(G)
 NAMES = ["soup20k_primary", "soup20k_adversarial", "cornell_camera", "cornell_adversarial", "sheets_adversarial",
-         "instanced_primary", "instanced_adversarial"]
+         "instanced_primary", "instanced_adversarial", "patches_primary", "patches_adversarial"]
 
 
 @pytest.mark.parametrize("name", NAMES)
@@ -25,10 +25,10 @@ def test_gpu_matches_golden(P, name):
     gold = G.load(name)
     agg = P.B200Aggregate(sc)
     hits = agg.IntersectClosest(rays)
-    assert hit_mismatches(hits, gold["hits"]).sum() == 0
+    assert hit_mismatches(hits, gold["hits"], sc).sum() == 0
     assert np.array_equal(agg.IntersectShadow(rays), gold["occ"])
     sh = P.scenes.shadow_rays(rays, gold["hits"], seed=35)
-    assert hit_mismatches(agg.IntersectClosest(sh), gold["shadow_hits"]).sum() == 0
+    assert hit_mismatches(agg.IntersectClosest(sh), gold["shadow_hits"], sc).sum() == 0
     assert np.array_equal(agg.IntersectShadow(sh), gold["shadow_occ"])
     if not sc.instances:
         assert np.array_equal(agg.Bounds().reshape(-1),
@@ -72,6 +72,31 @@ def test_gpu_instances_match_reference(P, refrun):
         ref_sh, _ = rs.closest(sh)
         occ_sh, _ = rs.any(sh)
         assert hit_mismatches(own.IntersectClosest(sh), ref_sh).sum() == 0
+        assert (own.IntersectShadow(sh) != occ_sh).sum() == 0
+    own.close()
+    given.close()
+
+
+def test_gpu_bilinear_patches_match_reference(P, refrun):
+    """Bilinear patches: 60 K twisted / planar / axis-aligned patches mixed with 30 K triangles; the
+    library's own tree and the tree read out of the reference (prims of kind 2); (u, v) and t bit-exact."""
+    sc = P.scenes.patch_scene(60000, 30000, seed=97)
+    rs = refrun.RefScene(sc)
+    own = P.B200Aggregate(sc)
+    given = P.B200Aggregate(sc, bvhs=rs.dump_bvh())
+    kinds = np.array([m.kind for m in sc.meshes] + [0])
+    for rays in (P.scenes.primary_rays(1 << 19, seed=5), P.scenes.adversarial_rays(sc, 1 << 17, seed=6)):
+        ref, _ = rs.closest(rays)
+        mine = own.IntersectClosest(rays)
+        assert (kinds[np.minimum(ref["mesh"], len(sc.meshes))] == 1).mean() > 0.2
+        assert hit_mismatches(mine, ref, sc).sum() == 0
+        assert np.array_equal(mine.view("u1"), given.IntersectClosest(rays).view("u1"))
+        occ_ref, _ = rs.any(rays)
+        assert (own.IntersectShadow(rays) != occ_ref).sum() == 0
+        sh = P.scenes.shadow_rays(rays, mine)
+        ref_sh, _ = rs.closest(sh)
+        occ_sh, _ = rs.any(sh)
+        assert hit_mismatches(own.IntersectClosest(sh), ref_sh, sc).sum() == 0
         assert (own.IntersectShadow(sh) != occ_sh).sum() == 0
     own.close()
     given.close()
