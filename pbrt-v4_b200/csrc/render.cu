@@ -11,6 +11,8 @@
 //            -> finish -> film.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 #include "render_core.h"
 #include "render_kernels.h"
 
@@ -473,6 +475,10 @@ ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth, int kind) {
     ray[6] = -1.f;
 }
 
+}  // namespace b200pt
+#include "render_volume_warp.cuh"
+namespace b200pt {
+
 // ---- unoccluded light samples join the path's radiance (RecordShadowRayResult, wavefront/intersect.h:176-190)
 __global__ void __launch_bounds__(256)
 ResolveShadowKernel(PassBuffers pb, int depth) {
@@ -610,11 +616,20 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
 #undef B2_SHADE
     return cudaGetLastError();
 }
+constexpr int kVolWarpGrid = 148 * 16;  // persistent-style grid of the warp-per-ray kernels (stride loop over the list)
+
 cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width, int nActive,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, bool warpPerRay) {
     int grid = Blocks(nActive, kShadeBlock);
     VolSortKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth, 0);
-    for (int kind = 0; kind < 2; ++kind) {
+    for (int kind = 0; kind < 2 && warpPerRay; ++kind) {
+        int g = (int)std::min<long long>(kVolWarpGrid, Blocks(nActive, kVolWarpBlock / 32));
+        if (rs.integrator.lightSampler == 2)
+            VolMediumWarpKernel<1><<<g, kVolWarpBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+        else
+            VolMediumWarpKernel<0><<<g, kVolWarpBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+    }
+    for (int kind = 0; kind < 2 && !warpPerRay; ++kind) {
         if (rs.integrator.lightSampler == 2)
             VolMediumKernel<1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
         else
@@ -622,13 +637,20 @@ cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int
     }
     return cudaGetLastError();
 }
-cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {
+cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream,
+                           bool warpPerRay) {
     // counts[2..4] of this iteration: the material queues are spent, the slots hold the walk queues' lengths
     cudaError_t e = cudaMemsetAsync(pb.counts + kCountStride * depth + 2, 0, 3 * sizeof(int), stream);
     if (e != cudaSuccess) return e;
     VolSortKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth, 1);
-    for (int kind = 0; kind < 3; ++kind)
-        ShadowTrKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
+    for (int kind = 0; kind < 3; ++kind) {
+        // walks outside any medium (kind 0) only tell occluders from interfaces: a thread per ray is the better fit
+        if (warpPerRay && kind > 0)
+            ShadowTrWarpKernel<<<(int)std::min<long long>(kVolWarpGrid, Blocks(nActive, kVolWarpBlock / 32)), kVolWarpBlock, 0,
+                                 stream>>>(rs, pb, depth, kind);
+        else
+            ShadowTrKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
+    }
     return cudaGetLastError();
 }
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {

@@ -37,6 +37,7 @@ struct b200pt_render {
     int nPixels = 0;
     size_t filmDoubles = 0;  // 4 per pixel, + 2 * nBuckets per pixel for a spectral film
     long long maxPathsPerPass = 4ll << 20;    // B200PT_PASS_PATHS overrides
+    bool volWarp = false;                     // B200PT_VOL_KERNEL=warp: the warp-per-ray volume kernels (measured slower)
     b200pt_render_stats stats{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
@@ -138,6 +139,7 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         if (m.material < 0) r->matMask |= 1u;  // null materials go through the diffuse queue, which ends the path
     if (r->matMask == 0) r->matMask = 1;
     if (const char *v = getenv("B200PT_PASS_PATHS")) r->maxPathsPerPass = std::max(1ll, atoll(v));
+    if (const char *v = getenv("B200PT_VOL_KERNEL")) r->volWarp = std::string(v) == "warp";
     r->filmDoubles = size_t(r->nPixels) * (4 + 2 * size_t(r->dev.film.nBuckets));
     if (cudaMalloc((void **)&r->dFilm, sizeof(double) * r->filmDoubles) != cudaSuccess ||
         cudaMalloc((void **)&r->dImage, sizeof(float) * std::max(3, r->dev.film.nBuckets) * size_t(r->nPixels)) != cudaSuccess ||
@@ -218,7 +220,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                                                    ctx->nodeMin, ctx->stream, true, nRays));
                 ++launches;
                 if (r->dev.nMedia) {
-                    B2_CUDA(ctx, LaunchVolMedium(r->dev, pb, j, nPix, width, nActive, ctx->stream));
+                    B2_CUDA(ctx, LaunchVolMedium(r->dev, pb, j, nPix, width, nActive, ctx->stream, r->volWarp));
                     launches += 3;
                 }
                 B2_CUDA(ctx, LaunchClassify(r->dev, pb, j, nActive, ctx->stream));
@@ -236,7 +238,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                     B2_CUDA(ctx, LaunchTraversePersist(sc, pb.shRays, hc[0], (b200pt_hit *)pb.shHits, nullptr, false,
                                                        r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
                                                        ctx->nodeMin, ctx->stream, true, nShadow));
-                    B2_CUDA(ctx, LaunchShadowTr(r->dev, pb, j, hc[0], ctx->stream));
+                    B2_CUDA(ctx, LaunchShadowTr(r->dev, pb, j, hc[0], ctx->stream, r->volWarp));
                     launches += 5;
                     B2_CUDA(ctx, cudaMemcpyAsync(&live, pb.shContinue, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
                     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -85,6 +85,7 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
 template <class IO>
 B2_HD bool AnyOf(const IO &io, int which) {
     bool any = false;
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) any |= (which == 0 ? io.Beta(k) : io.Ru(k)) != 0;
     return any;
 }
@@ -108,6 +109,7 @@ B2_HD int VolMediumStep(const RenderSceneDev &rs, PathRegs &p, float tHit, IO &i
     SampleTMaj(m, sigT, p.rayO, p.rayD, tHit, u, rng, T_maj, cb);
     if (cb.terminated || !AnyOf(io, 0) || !AnyOf(io, 1)) return VOL_TERMINATED;
     if (!cb.scattered) {
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) {
             float f = T_maj[k] / T_maj[0];
             io.SetBeta(k, io.Beta(k) * f);
@@ -135,6 +137,7 @@ B2_HD int VolMediumStep(const RenderSceneDev &rs, PathRegs &p, float tHit, IO &i
             bool anyL = false;
             io.ShadowBegin();
             LambdaIter li(p.lambdaU);
+B2_SPECTRAL_LOOP
             for (int k = 0; k < kNLambda; ++k, li.Next()) {
                 float Le = light.scale * SpectrumAt(sp, li.lam) * lp.atten;
                 io.SetLd(k, io.Beta(k) * fHat * Le);
@@ -157,6 +160,7 @@ B2_HD int VolMediumStep(const RenderSceneDev &rs, PathRegs &p, float tHit, IO &i
     float pdf;
     V3 wi = SampleHenyeyGreenstein(-p.rayD, m.g, u0, u1, &pdf);
     if (pdf == 0) return VOL_TERMINATED;
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) {
         io.SetBeta(k, io.Beta(k) * (pdf / pdf));
         io.SetRl(k, io.Ru(k) / pdf);
@@ -199,6 +203,7 @@ B2_HD int ShadowTrSegment(const RenderSceneDev &rs, float lambdaU, ShadowRegs &s
         MediumSpectra(rs, m, lambdaU, sigA, sigS, sigT);
         ShadowMediumCB cb(sh.rng, sigA, sigS, sigT, T_ray, r_l, r_u);
         SampleTMaj(m, sigT, sh.o, sh.d, tMax, u, sh.rng, T_maj, cb);
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) {
             float f = T_maj[k] / T_maj[0];
             T_ray[k] *= f;
@@ -207,6 +212,7 @@ B2_HD int ShadowTrSegment(const RenderSceneDev &rs, float lambdaU, ShadowRegs &s
         }
     }
     bool any = false;
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) any |= T_ray[k] != 0;
     if (!any) return SHADOW_BLOCKED;
     if (!isHit) return SHADOW_REACHED;
@@ -226,12 +232,14 @@ template <class LdFn, class RpFn, class AddFn>
 B2_HD void ShadowTrFinish(const float *T_ray, const float *r_l, const float *r_u, float p_l, float scatterPDF, LdFn Ld,
                           RpFn r_p, AddFn add) {
     float sum = 0;
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) {
         float rp = r_p(k);
         float a = r_l[k] * (rp * p_l), b = r_u[k] * (rp * scatterPDF);
         sum = k == 0 ? a + b : sum + (a + b);
     }
     float avg = sum / kNLambda;
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) add(k, Ld(k) * T_ray[k] / avg);
 }
 

@@ -8,6 +8,14 @@
 #include "instance.h"
 #include "render_layered.h"
 
+#ifndef B2_SPECTRAL_LOOP  // keep the 31-trip loops rolled on the device (render_path.h says why)
+#if defined(__CUDA_ARCH__)
+#define B2_SPECTRAL_LOOP _Pragma("unroll 2")
+#else
+#define B2_SPECTRAL_LOOP
+#endif
+#endif
+
 namespace b200pt {
 
 constexpr float kInv4Pi = 0.07957747154594766788f;
@@ -200,6 +208,7 @@ B2_HD void SampleTMaj(const MediumDev &m, const float *sigT, V3 ro, V3 rd, float
     tMax *= Length(rd);
     rd = Normalize(rd);
     MajorantIter it = MediumSampleRay(m, ro, rd, tMax);
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
     bool done = false;
     while (!done) {
@@ -209,6 +218,7 @@ B2_HD void SampleTMaj(const MediumDev &m, const float *sigT, V3 ro, V3 rd, float
         if (sigMaj0 == 0) {
             float dt = seg.tMax - seg.tMin;
             if (std::isinf(dt)) dt = 3.402823466e+38f;
+B2_SPECTRAL_LOOP
             for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(-dt * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
             continue;
         }
@@ -218,22 +228,26 @@ B2_HD void SampleTMaj(const MediumDev &m, const float *sigT, V3 ro, V3 rd, float
             u = PcgFloat(rng);
             if (t < seg.tMax) {
                 const float nd = -(t - tMin);
+B2_SPECTRAL_LOOP
                 for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(nd * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
                 V3 p = ro + rd * t;
                 if (!cb(p, MediumDensityAt(m, p), m.type == 0 ? 1.f : seg.scale, T_maj)) {
                     done = true;
                     break;
                 }
+B2_SPECTRAL_LOOP
                 for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
                 tMin = t;
             } else {
                 float dt = seg.tMax - tMin;
                 if (std::isinf(dt)) dt = 3.402823466e+38f;
+B2_SPECTRAL_LOOP
                 for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(-dt * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
                 break;
             }
         }
     }
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
 }
 
@@ -255,6 +269,7 @@ B2_HD int SampleDiscrete3(float w0, float w1, float w2, float u) {
 // The medium's spectra at the path's wavelengths
 B2_HD void MediumSpectra(const RenderSceneDev &rs, const MediumDev &m, float lambdaU, float *sigA, float *sigS, float *sigT) {
     LambdaIter li(lambdaU);
+B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k, li.Next()) {
         sigA[k] = MediumSigmaA(rs, m, li.lam);
         sigS[k] = MediumSigmaS(rs, m, li.lam);
@@ -278,11 +293,13 @@ struct PathMediumCB {
         : io(i), rng(r), sigA(a), sigS(s), sigT(t), depth(d), maxDepth(md) { pScatter = mk(0, 0, 0); }
     B2_HD bool AnyBeta() const {
         bool any = false;
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) any |= io.Beta(k) != 0;
         return any;
     }
     B2_HD bool AnyRu() const {
         bool any = false;
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) any |= io.Ru(k) != 0;
         return any;
     }
@@ -307,6 +324,7 @@ struct PathMediumCB {
                 return false;
             }
             float pdf = T_maj[0] * (sigS[0] * density);
+B2_SPECTRAL_LOOP
             for (int k = 0; k < kNLambda; ++k) {
                 float f = T_maj[k] * (sigS[k] * density) / pdf;
                 io.SetBeta(k, io.Beta(k) * f);
@@ -319,6 +337,7 @@ struct PathMediumCB {
             return false;
         }
         float pdf = 0;
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) {
             float sigMaj = sigT[k] * majScale;
             float sigN = fmaxf(0.f, sigMaj - sigA[k] * density - sigS[k] * density);  // ClampZero
@@ -341,6 +360,7 @@ struct ShadowMediumCB {
     B2_HD bool operator()(V3, float density, float majScale, const float *T_maj) {
         float pdf = T_maj[0] * (sigT[0] * majScale);
         float avg = 0, maxTr = 0;
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) {
             float sigMaj = sigT[k] * majScale;
             float sigN = fmaxf(0.f, sigMaj - sigA[k] * density - sigS[k] * density);
@@ -350,15 +370,19 @@ struct ShadowMediumCB {
             avg += r_l[k] + r_u[k];
         }
         avg /= kNLambda;  // SampledSpectrum::Average: sum / N
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) maxTr = k == 0 ? T_ray[0] / avg : fmaxf(maxTr, T_ray[k] / avg);
         bool any = false;
         if (maxTr < 0.05f) {
             const float q = 0.75f;
             if (PcgFloat(rng) < q)
+B2_SPECTRAL_LOOP
                 for (int k = 0; k < kNLambda; ++k) T_ray[k] = 0.f;
             else
+B2_SPECTRAL_LOOP
                 for (int k = 0; k < kNLambda; ++k) T_ray[k] /= 1 - q;
         }
+B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) any |= T_ray[k] != 0;
         return any;
     }

@@ -237,3 +237,21 @@ def test_config5_volpath(P, rendercheck):
         r.close()
     cpu0 = P.render.film_to_image(rendercheck(clear), clear.d["film_matrix"])
     assert rrmse(img0, cpu0) <= 1e-4
+
+
+def test_volume_kernels_warp_per_ray_equals_thread_per_ray(P, monkeypatch):
+    """The alternative volume kernels (one warp per ray, one lane per wavelength, B200PT_VOL_KERNEL=warp) against
+    the default thread-per-ray kernels, which run the host+device headers the CPU check is made of: the same
+    film, bit for bit."""
+    rsc = P.RenderScene.load(os.path.join(GOLD, "config5_small.b2rs"))
+    films = []
+    for mode in ("thread", "warp"):
+        monkeypatch.setenv("B200PT_VOL_KERNEL", mode)
+        r = P.B200Renderer(rsc)
+        try:
+            r.render()
+            films.append(r.film().copy())
+        finally:
+            r.close()
+    assert films[0][..., :3].sum() > 0
+    assert np.array_equal(films[0], films[1])
