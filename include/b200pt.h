@@ -191,7 +191,8 @@ typedef struct b200pt_material {
     float params[8];
 } b200pt_material;
 
-/* DiffuseAreaLight on one triangle (lights.h:407-500) or a UniformInfiniteLight (lights.h:512-554:
+/* DiffuseAreaLight on one triangle or one bilinear patch (lights.h:407-500; `tri` is then the patch index of a
+ * B200PT_MESH_BILINEAR mesh, sampled as BilinearPatch::Sample, shapes.cpp:1158-1372) or a UniformInfiniteLight (lights.h:512-554:
  * spectrum + scale only; mesh/tri unused) + its PowerLightSampler alias-table bin
  * (lightsamplers.cpp:76-96, util/sampling.cpp:562-617).  Order = the host's `lights` vector. */
 enum { B200PT_LIGHT_AREA_TRIANGLE = 0, B200PT_LIGHT_UNIFORM_INFINITE = 1 };

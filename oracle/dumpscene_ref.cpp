@@ -354,8 +354,12 @@ int main(int argc, char **argv) {
     // ---- geometry: walk the top-level BVH's ordered primitives (triangles only)
     if (!accel.Is<BVHAggregate>()) die("top-level aggregate is not a BVH");
     const BVHAggregate *bvh = accel.Cast<BVHAggregate>();
+    // mesh ids: the triangle meshes first, the bilinear patch meshes after them
     const auto &allMeshes = *Triangle::allMeshes;
-    size_t nMesh = allMeshes.size();
+    const size_t nTriMeshes = allMeshes.size();
+    const size_t nPatchMeshes = BilinearPatch::allMeshes ? BilinearPatch::allMeshes->size() : 0;
+    auto patchMesh = [&](size_t m) { return (*BilinearPatch::allMeshes)[m - nTriMeshes]; };
+    size_t nMesh = nTriMeshes + nPatchMeshes;
     std::vector<int32_t> meshAttr(nMesh * 3, -1);
     std::vector<const void *> meshMaterial(nMesh, nullptr);
     std::map<const void *, int> materialId;
@@ -379,12 +383,35 @@ int main(int argc, char **argv) {
             mtl = gp->material;
             area = gp->areaLight;
             if (gp->alpha) die("alpha textures are not dumped");
-            if (volpath && gp->mediumInterface.IsMediumTransition())
-                meshMediaOf[shape.Cast<Triangle>()->meshIndex] = {mediumIndex(gp->mediumInterface.inside),
-                                                                  mediumIndex(gp->mediumInterface.outside)};
+            if (volpath && gp->mediumInterface.IsMediumTransition()) {
+                int mm = shape.Is<Triangle>() ? shape.Cast<Triangle>()->meshIndex
+                                              : int(nTriMeshes) + shape.Cast<BilinearPatch>()->meshIndex;
+                meshMediaOf[mm] = {mediumIndex(gp->mediumInterface.inside), mediumIndex(gp->mediumInterface.outside)};
+            }
         } else
-            die("only triangle primitives are dumped so far");
-        if (!shape.Is<Triangle>()) die("only triangles are dumped so far");
+            die("only triangle and bilinear patch primitives are dumped so far");
+        if (const BilinearPatch *bp = shape.CastOrNullptr<BilinearPatch>()) {
+            int m = int(nTriMeshes) + bp->meshIndex;
+            primsOut.insert(primsOut.end(), {2u, uint32_t(m), uint32_t(bp->blpIndex)});
+            if (mtl && !materialId.count(mtl.ptr())) {
+                materialId[mtl.ptr()] = int(materialList.size());
+                materialList.push_back(mtl);
+            }
+            if (meshObject[m] != -1 && meshObject[m] != object) die("mesh used by two object definitions");
+            meshObject[m] = object;
+            meshAttr[3 * m + 0] = mtl ? materialId[mtl.ptr()] : -1;
+            meshAttr[3 * m + 2] = (patchMesh(m)->reverseOrientation ^ patchMesh(m)->transformSwapsHandedness) ? 1 : 0;
+            if (area) {
+                int li = lightIndex.at(area.ptr());
+                lightMeshTri[2 * li] = m;
+                lightMeshTri[2 * li + 1] = bp->blpIndex;
+                int first = li - bp->blpIndex;
+                if (meshAttr[3 * m + 1] != -1 && meshAttr[3 * m + 1] != first) die("area lights of a mesh are not consecutive");
+                meshAttr[3 * m + 1] = first;
+            }
+            return;
+        }
+        if (!shape.Is<Triangle>()) die("only triangles and bilinear patches are dumped so far");
         const Triangle *t = shape.Cast<Triangle>();
         int m = t->meshIndex;
         primsOut.insert(primsOut.end(), {0u, uint32_t(m), uint32_t(t->triIndex)});
@@ -466,7 +493,7 @@ int main(int argc, char **argv) {
             if (used[m]) memcpy(&attr2[3 * meshRemap[m]], &meshAttr[3 * m], 12);
         meshAttr.swap(attr2);
         for (size_t i = 0; i < bvhPrims.size(); i += 3)
-            if (bvhPrims[i] == 0) bvhPrims[i + 1] = meshRemap[bvhPrims[i + 1]];
+            if (bvhPrims[i] != 1) bvhPrims[i + 1] = meshRemap[bvhPrims[i + 1]];
         for (auto &op : objPrims)
             for (size_t i = 0; i < op.size(); i += 3) op[i + 1] = meshRemap[op[i + 1]];
         std::vector<int32_t> mo2(next);
@@ -480,9 +507,22 @@ int main(int argc, char **argv) {
     nMesh = meshAttr.size() / 3;
     std::vector<uint32_t> nv, nt;
     std::vector<float> P;
-    std::vector<int32_t> idx;
+    std::vector<int32_t> idx, patchIdx;
+    std::vector<uint32_t> meshKind;
     for (size_t m = 0; m < nMeshAll; ++m) {
         if (meshRemap[m] < 0) continue;
+        if (m >= nTriMeshes) {
+            const BilinearPatchMesh *mesh = patchMesh(m);
+            if (mesh->n || mesh->uv) fprintf(stderr, "dumpscene_ref: note: per-vertex n/uv of patch mesh %zu ignored\n", m);
+            if (mesh->imageDistribution) die("image-distributed patch emission is not dumped");
+            nv.push_back(mesh->nVertices);
+            nt.push_back(mesh->nPatches);
+            meshKind.push_back(1);
+            for (int i = 0; i < mesh->nVertices; ++i) P.insert(P.end(), {mesh->p[i].x, mesh->p[i].y, mesh->p[i].z});
+            patchIdx.insert(patchIdx.end(), mesh->vertexIndices, mesh->vertexIndices + 4 * mesh->nPatches);
+            continue;
+        }
+        meshKind.push_back(0);
         const TriangleMesh *mesh = allMeshes[m];
         if (mesh->n || mesh->uv || mesh->s) fprintf(stderr, "dumpscene_ref: note: per-vertex n/uv/s of mesh %zu ignored\n", m);
         nv.push_back(mesh->nVertices);
@@ -494,6 +534,11 @@ int main(int argc, char **argv) {
     w.u32("mesh_ntris", {uint32_t(nMesh)}, nt);
     w.f32("P", {uint32_t(P.size() / 3), 3}, P);
     w.i32("indices", {uint32_t(idx.size() / 3), 3}, idx);
+    if (!patchIdx.empty()) {
+        // mesh_kind 1 = bilinear patch mesh: its mesh_ntris patches take 4 indices each (p00 p10 p01 p11) from patch_indices
+        w.u32("mesh_kind", {uint32_t(nMesh)}, meshKind);
+        w.i32("patch_indices", {uint32_t(patchIdx.size() / 4), 4}, patchIdx);
+    }
     w.i32("mesh_attr", {uint32_t(nMesh), 3}, meshAttr);
     w.i32("mesh_object", {uint32_t(nMesh)}, meshObject);
     if (volpath) {

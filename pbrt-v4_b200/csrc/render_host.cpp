@@ -25,7 +25,6 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         return B200PT_ERR_INVALID;
     };
     if (!d) return bad("null render description");
-    if (hs.hasPatches) return bad("the render path takes triangle meshes only so far (bilinear patches: traversal entry points)");
     if (d->camera_type > 1) return bad("unsupported camera type (0 perspective, 1 realistic)");
     if (d->camera_type == 1) {
         if (d->n_lens_elements < 1 || d->n_lens_elements > 64 || !d->lens_elements)

@@ -6,7 +6,8 @@ namespace b200pt {
 
 struct TriVerts {
     V3 p0, p1, p2;
-    uint32_t mesh, tri;
+    V3 p3;  // bilinear patch: p00 p10 p01 p11 in p0..p3 (the mesh's index order)
+    uint32_t mesh, tri, kind;
 };
 B2_HD TriVerts LoadTri(const void *prims, uint32_t slot) {
     const PrimSlot *s = reinterpret_cast<const PrimSlot *>(prims) + slot;
@@ -14,8 +15,10 @@ B2_HD TriVerts LoadTri(const void *prims, uint32_t slot) {
     t.p0 = mk(s->p0[0], s->p0[1], s->p0[2]);
     t.p1 = mk(s->p1[0], s->p1[1], s->p1[2]);
     t.p2 = mk(s->p2[0], s->p2[1], s->p2[2]);
+    t.p3 = mk(s->p3[0], s->p3[1], s->p3[2]);
     t.mesh = s->mesh;
     t.tri = s->tri;
+    t.kind = s->kind;
     return t;
 }
 
@@ -61,6 +64,34 @@ B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b
     h.dpdus = dpdu;
     h.wo = Normalize(wo);  // Interaction constructor (interaction.h:36-41)
     return h;
+}
+
+// BilinearPatch::InteractionFromIntersection (shapes.h:1396-1500) for meshes without per-vertex uv / n: the point and
+// both partial derivatives are lerps of the four corners at the hit's (u,v); the normal is their cross product.
+B2_HD_CALL SurfHit PatchInteraction(const TriVerts &t, float u, float v, V3 wo, bool flipNormal) {
+    SurfHit h;
+    const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
+    V3 e0 = (1 - v) * p00 + v * p01, e1 = (1 - v) * p10 + v * p11;
+    V3 p = (1 - u) * e0 + u * e1;
+    V3 dpdu = e1 - e0;
+    V3 dpdv = ((1 - u) * p01 + u * p11) - ((1 - u) * p00 + u * p10);
+    V3 pAbsSum = Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11);
+    h.pi = MakeP3i(p, GammaF(6) * pAbsSum);
+    h.u = u;
+    h.v = v;
+    V3 n = Normalize(Cross(dpdu, dpdv));
+    if (flipNormal) n = -n;
+    h.n = n;
+    h.ns = n;
+    h.dpdus = dpdu;
+    h.wo = Normalize(wo);
+    return h;
+}
+
+// Shape::Intersect's interaction for either kind of slot; (b1, b2) of a patch record are its (u, v)
+B2_HD SurfHit SlotInteraction(const TriVerts &t, float b0, float b1, float b2, V3 wo, bool flipNormal) {
+    if (t.kind == 1) return PatchInteraction(t, b1, b2, wo, flipNormal);
+    return TriangleInteraction(t, b0, b1, b2, wo, flipNormal);
 }
 
 // Transform::operator()(SurfaceInteraction) for an object instance (util/transform.cpp:227-258,
@@ -283,6 +314,260 @@ B2_HD ShapeSampleOut SampleTriangleSolidAngle(const TriVerts &t, const LightCtx 
     return o;
 }
 
+// ---- emissive bilinear patches: BilinearPatch::Sample / PDF (shapes.cpp:1158-1372)
+
+// BilinearPatch::IsRectangle (shapes.h:1510-1532)
+B2_HD bool PatchIsRectangle(const TriVerts &t) {
+    const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
+    auto same = [](V3 a, V3 b) { return a.x == b.x && a.y == b.y && a.z == b.z; };
+    if (same(p00, p01) || same(p01, p11) || same(p11, p10) || same(p10, p00)) return false;
+    V3 n = Normalize(Cross(p10 - p00, p01 - p00));
+    if (AbsDotN(Normalize(p11 - p00), n) > 1e-5f) return false;
+    V3 pc = (p00 + p01 + p10 + p11) / 4.f;
+    float d2[4] = {LengthSquared(p00 - pc), LengthSquared(p01 - pc), LengthSquared(p10 - pc), LengthSquared(p11 - pc)};
+    for (int i = 1; i < 4; ++i)
+        if (fabsf(d2[i] - d2[0]) / d2[0] > 1e-4f) return false;
+    return true;
+}
+
+// SphericalQuadArea (util/vecmath.h:1648-1666)
+B2_HD float SphericalQuadArea(V3 a, V3 b, V3 c, V3 d) {
+    V3 axb = Cross(a, b), bxc = Cross(b, c), cxd = Cross(c, d), dxa = Cross(d, a);
+    if (LengthSquared(axb) == 0 || LengthSquared(bxc) == 0 || LengthSquared(cxd) == 0 || LengthSquared(dxa) == 0) return 0;
+    axb = Normalize(axb);
+    bxc = Normalize(bxc);
+    cxd = Normalize(cxd);
+    dxa = Normalize(dxa);
+    float alpha = AngleBetween(dxa, -axb), beta = AngleBetween(axb, -bxc);
+    float gamma = AngleBetween(bxc, -cxd), delta = AngleBetween(cxd, -dxa);
+    return fabsf(alpha + beta + gamma + delta - 2 * kPi);
+}
+
+// the local frame and corner geometry both spherical-rectangle routines start from (util/sampling.cpp:166-186, 228-262)
+struct SphRect {
+    V3 rx, ry, rz;
+    float x0, y0, z0, x1, y1;
+    float g0, g1, g2, g3, b0, b1;
+};
+B2_HD SphRect SphRectInit(V3 pRef, V3 s, V3 ex, V3 ey) {
+    SphRect q;
+    float exl = Length(ex), eyl = Length(ey);
+    q.rx = ex / exl;
+    q.ry = ey / eyl;
+    q.rz = Cross(q.rx, q.ry);
+    V3 d = s - pRef;
+    q.x0 = Dot(d, q.rx);
+    q.y0 = Dot(d, q.ry);
+    q.z0 = Dot(d, q.rz);
+    if (q.z0 > 0) {
+        q.rz = -q.rz;
+        q.z0 *= -1;
+    }
+    q.x1 = q.x0 + exl;
+    q.y1 = q.y0 + eyl;
+    V3 v00 = mk(q.x0, q.y0, q.z0), v01 = mk(q.x0, q.y1, q.z0), v10 = mk(q.x1, q.y0, q.z0), v11 = mk(q.x1, q.y1, q.z0);
+    V3 n0 = Normalize(Cross(v00, v10)), n1 = Normalize(Cross(v10, v11));
+    V3 n2 = Normalize(Cross(v11, v01)), n3 = Normalize(Cross(v01, v00));
+    q.g0 = AngleBetween(-n0, n1);
+    q.g1 = AngleBetween(-n1, n2);
+    q.g2 = AngleBetween(-n2, n3);
+    q.g3 = AngleBetween(-n3, n0);
+    q.b0 = n0.z;
+    q.b1 = n2.z;
+    return q;
+}
+
+// SampleSphericalRectangle (util/sampling.cpp:163-220)
+B2_HD V3 SampleSphericalRectangle(V3 pRef, V3 s, V3 ex, V3 ey, float u0, float u1, float *pdf) {
+    SphRect q = SphRectInit(pRef, s, ex, ey);
+    float solidAngle = q.g0 + q.g1 + q.g2 + q.g3 - 2 * kPi;
+    if (solidAngle <= 0) {
+        *pdf = 0;
+        return s + u0 * ex + u1 * ey;
+    }
+    *pdf = fmaxf(0.f, 1 / solidAngle);
+    if (solidAngle < 1e-3f) return s + u0 * ex + u1 * ey;
+    float au = u0 * (q.g0 + q.g1 - 2 * kPi) + (u0 - 1) * (q.g2 + q.g3);
+    float fu = (cosf(au) * q.b0 - q.b1) / sinf(au);
+    float cu = copysignf(1 / sqrtf(SqrF(fu) + SqrF(q.b0)), fu);
+    cu = Clampf(cu, -kOneMinusEps, kOneMinusEps);
+    float xu = -(cu * q.z0) / SafeSqrt(1 - SqrF(cu));
+    xu = Clampf(xu, q.x0, q.x1);
+    float dd = sqrtf(SqrF(xu) + SqrF(q.z0));
+    float h0 = q.y0 / sqrtf(SqrF(dd) + SqrF(q.y0));
+    float h1 = q.y1 / sqrtf(SqrF(dd) + SqrF(q.y1));
+    float hv = h0 + u1 * (h1 - h0), hvsq = SqrF(hv);
+    float yv = (hvsq < 1 - 1e-6f) ? (hv * dd) / sqrtf(1 - hvsq) : q.y1;
+    return pRef + (xu * q.rx + yv * q.ry + q.z0 * q.rz);
+}
+
+// InvertSphericalRectangleSample (util/sampling.cpp:222-344)
+B2_HD void InvertSphericalRectangleSample(V3 pRef, V3 s, V3 ex, V3 ey, V3 pRect, float &u0o, float &u1o) {
+    SphRect q = SphRectInit(pRef, s, ex, ey);
+    float z0sq = SqrF(q.z0), y0sq = SqrF(q.y0), y1sq = SqrF(q.y1);
+    float b0sq = SqrF(q.b0);
+    float solidAngle = float(double(q.g0) + double(q.g1) + double(q.g2) + double(q.g3) - 2. * double(kPi));
+    if (solidAngle < 1e-3f) {
+        V3 pq = pRect - s;
+        u0o = Dot(pq, ex) / LengthSquared(ex);
+        u1o = Dot(pq, ey) / LengthSquared(ey);
+        return;
+    }
+    V3 v = pRect - pRef;
+    float xu = Dot(v, q.rx), yv = Dot(v, q.ry);
+    xu = Clampf(xu, q.x0, q.x1);
+    if (xu == 0) xu = 1e-10f;
+    float invcusq = 1 + z0sq / SqrF(xu);
+    float fusq = invcusq - b0sq;
+    float fu = copysignf(sqrtf(fusq), xu);
+    float sq = SafeSqrt(DiffOfProducts(q.b0, q.b0, q.b1, q.b1) + fusq);
+    float au = atan2f(-(q.b1 * fu) - copysignf(q.b0 * sq, fu * q.b0), q.b0 * q.b1 - sq * fabsf(fu));
+    if (au > 0) au -= 2 * kPi;
+    if (fu == 0) au = kPi;
+    float u0 = (au + q.g2 + q.g3) / solidAngle;
+    float ddsq = SqrF(xu) + z0sq;
+    float dd = sqrtf(ddsq);
+    float h0 = q.y0 / sqrtf(ddsq + y0sq);
+    float h1 = q.y1 / sqrtf(ddsq + y1sq);
+    float yvsq = SqrF(yv);
+    float root = fabsf(h0 - h1) * sqrtf(yvsq * (ddsq + yvsq)) / (ddsq + yvsq);
+    float u1[2] = {(DiffOfProducts(h0, h0, h0, h1) - root) / SqrF(h0 - h1), (DiffOfProducts(h0, h0, h0, h1) + root) / SqrF(h0 - h1)};
+    float hv[2] = {Lerp(u1[0], h0, h1), Lerp(u1[1], h0, h1)};
+    float yz[2] = {(hv[0] * dd) / sqrtf(1 - SqrF(hv[0])), (hv[1] * dd) / sqrtf(1 - SqrF(hv[1]))};
+    u0o = Clampf(u0, 0, 1);
+    u1o = (fabsf(yz[0] - yv) < fabsf(yz[1] - yv)) ? u1[0] : u1[1];
+}
+
+// the corner weights of approximately uniform area sampling (shapes.cpp:1172-1175, 1241-1244)
+B2_HD void PatchAreaWeights(const TriVerts &t, float w[4]) {
+    const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
+    w[0] = Length(Cross(p10 - p00, p01 - p00));
+    w[1] = Length(Cross(p10 - p00, p11 - p10));
+    w[2] = Length(Cross(p01 - p00, p11 - p01));
+    w[3] = Length(Cross(p11 - p10, p11 - p01));
+}
+
+// BilinearPatch::Sample(u) by area (shapes.cpp:1158-1217), no image distribution, no per-vertex uv / n
+B2_HD ShapeSampleOut SamplePatchArea(const TriVerts &t, bool rectangle, float u0, float u1, bool flipNormal) {
+    ShapeSampleOut o;
+    o.ok = false;
+    const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
+    float pdf = 1, su = u0, sv = u1;
+    if (!rectangle) {
+        float w[4];
+        PatchAreaWeights(t, w);
+        SampleBilinear(u0, u1, w, su, sv);
+        pdf = BilinearPDF(su, sv, w);
+    }
+    V3 pu0 = (1 - sv) * p00 + sv * p01, pu1 = (1 - sv) * p10 + sv * p11;
+    V3 p = (1 - su) * pu0 + su * pu1;
+    V3 dpdu = pu1 - pu0;
+    V3 dpdv = ((1 - su) * p01 + su * p11) - ((1 - su) * p00 + su * p10);
+    if (LengthSquared(dpdu) == 0 || LengthSquared(dpdv) == 0) return o;
+    V3 n = Normalize(Cross(dpdu, dpdv));
+    if (flipNormal) n = -n;
+    V3 pAbsSum = Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11);
+    o.pi = MakeP3i(p, GammaF(6) * pAbsSum);
+    o.n = n;
+    o.pdf = pdf / Length(Cross(dpdu, dpdv));
+    o.ok = true;
+    return o;
+}
+
+B2_HD void PatchCosWeights(V3 v00, V3 v10, V3 v01, V3 v11, V3 ns, float w[4]) {  // shapes.cpp:1288-1292
+    w[0] = fmaxf(0.01f, AbsDotN(ns, v00));
+    w[1] = fmaxf(0.01f, AbsDotN(ns, v10));
+    w[2] = fmaxf(0.01f, AbsDotN(ns, v01));
+    w[3] = fmaxf(0.01f, AbsDotN(ns, v11));
+}
+
+constexpr float kPatchMinSphericalSampleArea = 1e-4f;  // shapes.h:1538
+
+// BilinearPatch::Sample(ctx, u) (shapes.cpp:1257-1330)
+B2_HD_CALL ShapeSampleOut SamplePatchSolidAngle(const TriVerts &t, const LightCtx &ctx, float u0, float u1, bool flipNormal) {
+    const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
+    V3 rp = Mid(ctx.pi);
+    V3 v00 = Normalize(p00 - rp), v10 = Normalize(p10 - rp), v01 = Normalize(p01 - rp), v11 = Normalize(p11 - rp);
+    bool rectangle = PatchIsRectangle(t);
+    if (!rectangle || SphericalQuadArea(v00, v10, v11, v01) <= kPatchMinSphericalSampleArea) {
+        ShapeSampleOut o = SamplePatchArea(t, rectangle, u0, u1, flipNormal);
+        if (!o.ok) return o;
+        V3 wi = Mid(o.pi) - rp;
+        if (LengthSquared(wi) == 0) {
+            o.ok = false;
+            return o;
+        }
+        wi = Normalize(wi);
+        o.pdf /= AbsDotN(o.n, -wi) / LengthSquared(rp - Mid(o.pi));
+        if (std::isinf(o.pdf)) o.ok = false;
+        return o;
+    }
+    ShapeSampleOut o;
+    float pdf = 1;
+    if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
+        float w[4], px, py;
+        PatchCosWeights(v00, v10, v01, v11, ctx.ns, w);
+        SampleBilinear(u0, u1, w, px, py);
+        u0 = px;
+        u1 = py;
+        pdf *= BilinearPDF(u0, u1, w);
+    }
+    V3 eu = p10 - p00, ev = p01 - p00;
+    float quadPDF;
+    V3 p = SampleSphericalRectangle(rp, p00, eu, ev, u0, u1, &quadPDF);
+    pdf *= quadPDF;
+    V3 n = Normalize(Cross(eu, ev));
+    if (flipNormal) n = -n;
+    o.pi = MakeP3i(p, mk(0, 0, 0));
+    o.n = n;
+    o.pdf = pdf;
+    o.ok = true;
+    return o;
+}
+
+// BilinearPatch::PDF(ctx, wi) (shapes.cpp:1332-1372) with PDF(intr) (:1219-1255)
+B2_HD_CALL float PatchPDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
+    const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
+    V3 rp = Mid(ctx.pi);
+    V3 o = OffsetRayOrigin(ctx.pi, ctx.n, wi);
+    RayCtx r;
+    RaySetup(r, o.x, o.y, o.z, wi.x, wi.y, wi.z);
+    float q00[3] = {p00.x, p00.y, p00.z}, q10[3] = {p10.x, p10.y, p10.z};
+    float q01[3] = {p01.x, p01.y, p01.z}, q11[3] = {p11.x, p11.y, p11.z};
+    float tt, u, v;
+    if (!BilinearHit(r, INFINITY, q00, q10, q01, q11, tt, u, v)) return 0;
+    V3 v00 = Normalize(p00 - rp), v10 = Normalize(p10 - rp), v01 = Normalize(p01 - rp), v11 = Normalize(p11 - rp);
+    bool rectangle = PatchIsRectangle(t);
+    float quadArea = SphericalQuadArea(v00, v10, v11, v01);
+    V3 pu0 = (1 - v) * p00 + v * p01, pu1 = (1 - v) * p10 + v * p11;
+    // isect->intr.p(): the midpoint of the interval point InteractionFromIntersection builds
+    V3 pHit = Mid(MakeP3i((1 - u) * pu0 + u * pu1, GammaF(6) * (Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11))));
+    if (!rectangle || quadArea <= kPatchMinSphericalSampleArea) {
+        float pdf = 1;
+        if (!rectangle) {
+            float w[4];
+            PatchAreaWeights(t, w);
+            pdf = BilinearPDF(u, v, w);
+        }
+        V3 dpdu = pu1 - pu0;
+        V3 dpdv = ((1 - u) * p01 + u * p11) - ((1 - u) * p00 + u * p10);
+        V3 nrm = Cross(dpdu, dpdv);
+        pdf = pdf / Length(nrm);
+        V3 n = Normalize(nrm);  // sign does not matter under AbsDot
+        (void)flipNormal;
+        pdf = pdf * (LengthSquared(rp - pHit) / AbsDotN(n, -wi));
+        return std::isinf(pdf) ? 0.f : pdf;
+    }
+    float pdf = 1 / quadArea;
+    if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
+        float w[4], iu0, iu1;
+        PatchCosWeights(v00, v10, v01, v11, ctx.ns, w);
+        InvertSphericalRectangleSample(rp, p00, p10 - p00, p01 - p00, pHit, iu0, iu1);
+        return BilinearPDF(iu0, iu1, w) * pdf;
+    }
+    return pdf;
+}
+
 // Triangle::PDF(ctx, wi) (shapes.h:1132-1172)
 B2_HD float TrianglePDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
     V3 rp = Mid(ctx.pi);
@@ -314,6 +599,16 @@ B2_HD float TrianglePDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flip
     return pdf;
 }
 
+
+// Shape::Sample(ctx, u) / Shape::PDF(ctx, wi) of the emitter in slot `t`
+B2_HD ShapeSampleOut SampleShapeSolidAngle(const TriVerts &t, const LightCtx &ctx, float u0, float u1, bool flipNormal) {
+    if (t.kind == 1) return SamplePatchSolidAngle(t, ctx, u0, u1, flipNormal);
+    return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal);
+}
+B2_HD float ShapePDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
+    if (t.kind == 1) return PatchPDF(t, ctx, wi, flipNormal);
+    return TrianglePDF(t, ctx, wi, flipNormal);
+}
 }  // namespace b200pt
 
 #include "render_path.h"

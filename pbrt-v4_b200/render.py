@@ -15,9 +15,15 @@ class RenderScene:
     def __init__(self, d):
         self.d = d
         nv, nt = d["mesh_nverts"].astype(np.int64), d["mesh_ntris"].astype(np.int64)
-        vo, to = np.concatenate([[0], np.cumsum(nv)]), np.concatenate([[0], np.cumsum(nt)])
+        # mesh_kind 1: a bilinear patch mesh, its patches' four indices each in patch_indices
+        kind = d["mesh_kind"].astype(np.int64) if "mesh_kind" in d else np.zeros(len(nv), np.int64)
+        vo = np.concatenate([[0], np.cumsum(nv)])
+        to = np.concatenate([[0], np.cumsum(nt * (kind == 0))])
+        po = np.concatenate([[0], np.cumsum(nt * (kind == 1))])
         obj = d["mesh_object"] if "mesh_object" in d else np.full(len(nv), -1, np.int32)
-        meshes = [scenes.Mesh(d["P"][vo[i]:vo[i + 1]], d["indices"][to[i]:to[i + 1]], object=int(obj[i]))
+        meshes = [scenes.Mesh(d["P"][vo[i]:vo[i + 1]],
+                              d["patch_indices"][po[i]:po[i + 1]] if kind[i] else d["indices"][to[i]:to[i + 1]],
+                              object=int(obj[i]), kind=int(kind[i]))
                   for i in range(len(nv))]
         insts = []
         if "instance_object" in d:

@@ -341,7 +341,7 @@ MATERIALS = {
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
                  boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
-                 film="rgb", nbuckets=31):
+                 film="rgb", nbuckets=31, patches=False):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -380,6 +380,17 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
         elif c is None:
             lines.append('  AreaLightSource "diffuse" "rgb L" [17 12 4]')
             lines.append('  Material "diffuse" "rgb reflectance" [0 0 0]')
+            if patches == "emissive":
+                # the ceiling emitter as ONE rectangular bilinear patch (spherical-rectangle sampling, shapes.cpp:1281-1330)
+                # and a twisted one-sided emissive patch in front of the back wall (area sampling, :1266-1280)
+                q = m.p[[0, 1, 3, 2]]
+                lines.append('  Shape "bilinearmesh" "integer indices" [0 1 2 3] "point3 P" ['
+                             + " ".join(repr(float(x)) for x in q.reshape(-1)) + ']')
+                lines += ['AttributeEnd', 'AttributeBegin', '  AreaLightSource "diffuse" "rgb L" [3 6 9]',
+                          '  Material "diffuse" "rgb reflectance" [0 0 0]', '  ReverseOrientation',
+                          '  Shape "bilinearmesh" "integer indices" [0 1 2 3] "point3 P" '
+                          '[0.3 0.55 0.93  0.5 0.5 0.97  0.32 0.8 0.97  0.52 0.75 0.9]', 'AttributeEnd']
+                continue
         else:
             lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
         lines.append('  ' + _mesh_pbrt(m))
@@ -402,6 +413,22 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
             lines += ['AttributeBegin', f'  AreaLightSource "diffuse" "rgb L" [{L[0]:.5g} {L[1]:.5g} {L[2]:.5g}]',
                       '  Material "diffuse" "rgb reflectance" [0 0 0]',
                       f'  Shape "trianglemesh" "point3 P" [{pts}] "integer indices" [0 1 2 0 2 3]', 'AttributeEnd']
+    if patches:
+        # two `bilinearmesh` shapes (shapes.cpp:1117-1200) of non-planar patches: a diffuse wavy sheet above the short
+        # box and a rough copper saddle by the left wall, the second under ReverseOrientation
+        def sheet(x0, x1, z0, z1, n, height):
+            g = np.linspace(0.0, 1.0, n + 1)
+            pts = [(x0 + (x1 - x0) * u, height(u, v), z0 + (z1 - z0) * v) for v in g for u in g]
+            idx = [k for j in range(n) for i in range(n)
+                   for k in (j * (n + 1) + i, j * (n + 1) + i + 1, (j + 1) * (n + 1) + i, (j + 1) * (n + 1) + i + 1)]
+            return (f'Shape "bilinearmesh" "integer indices" [{" ".join(map(str, idx))}] "point3 P" '
+                    f'[{" ".join(f"{float(c):.7g}" for pt in pts for c in pt)}]')
+        lines += ['AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.25 0.35 0.75]',
+                  '  ' + sheet(0.5, 0.92, 0.12, 0.55, 4, lambda u, v: 0.42 + 0.07 * np.sin(5.0 * u) * np.cos(4.0 * v) + 0.1 * u * v),
+                  'AttributeEnd',
+                  'AttributeBegin', '  ' + MATERIALS["conductor_rough"], '  ReverseOrientation',
+                  '  ' + sheet(0.05, 0.3, 0.1, 0.45, 1, lambda u, v: 0.75 + 0.18 * (2 * u - 1) * (2 * v - 1)),
+                  'AttributeEnd']
     if infinite is not None:
         lines.append(f'LightSource "infinite" "rgb L" [{infinite[0]} {infinite[1]} {infinite[2]}]')
     with open(path, "w") as f:

@@ -67,6 +67,10 @@ RENDER_CASES = {
     "cornell_spectral_r48_s16": dict(res=48, spp=16, maxdepth=5, film="spectral", nbuckets=31),
     "cornell_coated_r64_s16": dict(res=64, spp=16, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough")),
     "cornell_glass_r64_s16": dict(res=64, spp=16, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass")),
+    # bilinear patch meshes shaded (BilinearPatch::InteractionFromIntersection), one under ReverseOrientation
+    "cornell_patches_r64_s16": dict(res=64, spp=16, maxdepth=5, patches=True),
+    # emissive patches: a rectangle (sampled as a spherical rectangle) and a twisted patch (by area), light BVH
+    "cornell_patchlights_r64_s16": dict(res=64, spp=16, maxdepth=5, patches="emissive", lightsampler="bvh"),
 }
 # Cases whose gate is the Monte-Carlo noise floor (rRMSE(ours, ref) <= 1.25 x rRMSE(ref seed s,
 # ref seed s+1)) instead of path-for-path agreement: after a lossless specular bounce the reference's
@@ -132,7 +136,10 @@ def make_config5_goldens(P, refrun, out):
 
 def make_render_goldens(P, refrun, out):
     import tempfile
+    pick = os.environ.get("B200PT_GOLDEN_CASES")  # comma-separated names: regenerate only these image cases
     for name, kw in RENDER_CASES.items():
+        if pick and name not in pick.split(","):
+            continue
         with tempfile.TemporaryDirectory() as tmp:
             pbrt, pfm = os.path.join(tmp, name + ".pbrt"), os.path.join(tmp, name + ".pfm")
             P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
@@ -147,6 +154,8 @@ def make_render_goldens(P, refrun, out):
                 img2, _ = refrun.render(pbrt, pfm)
                 np.save(os.path.join(out, name + "_ref2.npy"), img2.astype(np.float32))
             print(name, img.shape, "mean", img.mean(axis=(0, 1)), f"{secs:.2f}s")
+    if pick:
+        return
     with tempfile.TemporaryDirectory() as tmp:
         pbrt, pfm = os.path.join(tmp, "c3.pbrt"), os.path.join(tmp, "c3.pfm")
         P.scenes.config3_pbrt(pbrt, out=pfm, **CONFIG3_FULL)
@@ -181,8 +190,9 @@ if __name__ == "__main__":
         sys.exit(0)
     if not any(a.startswith("--only=") for a in sys.argv):
         make_render_goldens(P, refrun, out)
-        make_config4_goldens(P, refrun, out)
-        make_config5_goldens(P, refrun, out)
+        if not os.environ.get("B200PT_GOLDEN_CASES"):
+            make_config4_goldens(P, refrun, out)
+            make_config5_goldens(P, refrun, out)
     if "--render-only" in sys.argv:
         sys.exit(0)
     only = [a.split("=", 1)[1].split(",") for a in sys.argv if a.startswith("--only=")]
