@@ -211,6 +211,11 @@ typedef struct b200pt_mesh_attr {
     int32_t material;    /* index into materials, -1 = interface (no BSDF) */
     int32_t light_first; /* index of the light on triangle 0, -1 if not emissive */
     uint32_t flip_normal; /* reverseOrientation ^ transformSwapsHandedness (util/mesh.h:42) */
+    /* TriangleMesh::n / ::uv (util/mesh.h:44-47) of a triangle mesh, one entry per triangle CORNER in index order
+     * (3 x 3 floats, 3 x 2 floats per triangle), or NULL: shading normals and the (u,v) parameterisation of
+     * Triangle::InteractionFromIntersection (shapes.h:884-1010).  Ignored for bilinear patch meshes. */
+    const float *corner_n;
+    const float *corner_uv;
 } b200pt_mesh_attr;
 
 /* One participating medium with a Henyey-Greenstein phase function and no emission.

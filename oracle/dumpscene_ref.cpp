@@ -508,7 +508,8 @@ int main(int argc, char **argv) {
     std::vector<uint32_t> nv, nt;
     std::vector<float> P;
     std::vector<int32_t> idx, patchIdx;
-    std::vector<uint32_t> meshKind;
+    std::vector<uint32_t> meshKind, meshHasN, meshHasUV;
+    std::vector<float> cornerN, cornerUV;
     for (size_t m = 0; m < nMeshAll; ++m) {
         if (meshRemap[m] < 0) continue;
         if (m >= nTriMeshes) {
@@ -518,13 +519,23 @@ int main(int argc, char **argv) {
             nv.push_back(mesh->nVertices);
             nt.push_back(mesh->nPatches);
             meshKind.push_back(1);
+            meshHasN.push_back(0);
+            meshHasUV.push_back(0);
             for (int i = 0; i < mesh->nVertices; ++i) P.insert(P.end(), {mesh->p[i].x, mesh->p[i].y, mesh->p[i].z});
             patchIdx.insert(patchIdx.end(), mesh->vertexIndices, mesh->vertexIndices + 4 * mesh->nPatches);
             continue;
         }
         meshKind.push_back(0);
         const TriangleMesh *mesh = allMeshes[m];
-        if (mesh->n || mesh->uv || mesh->s) fprintf(stderr, "dumpscene_ref: note: per-vertex n/uv/s of mesh %zu ignored\n", m);
+        if (mesh->s) die("per-vertex tangents (S) are not dumped");
+        // per-vertex normals / uv leave as per-corner arrays (3 per triangle), so the device needs no index buffer
+        meshHasN.push_back(mesh->n ? 1 : 0);
+        meshHasUV.push_back(mesh->uv ? 1 : 0);
+        for (int i = 0; i < 3 * mesh->nTriangles; ++i) {
+            int v = mesh->vertexIndices[i];
+            if (mesh->n) cornerN.insert(cornerN.end(), {mesh->n[v].x, mesh->n[v].y, mesh->n[v].z});
+            if (mesh->uv) cornerUV.insert(cornerUV.end(), {mesh->uv[v].x, mesh->uv[v].y});
+        }
         nv.push_back(mesh->nVertices);
         nt.push_back(mesh->nTriangles);
         for (int i = 0; i < mesh->nVertices; ++i) P.insert(P.end(), {mesh->p[i].x, mesh->p[i].y, mesh->p[i].z});
@@ -534,6 +545,12 @@ int main(int argc, char **argv) {
     w.u32("mesh_ntris", {uint32_t(nMesh)}, nt);
     w.f32("P", {uint32_t(P.size() / 3), 3}, P);
     w.i32("indices", {uint32_t(idx.size() / 3), 3}, idx);
+    if (!cornerN.empty() || !cornerUV.empty()) {
+        w.u32("mesh_has_n", {uint32_t(nMesh)}, meshHasN);
+        w.u32("mesh_has_uv", {uint32_t(nMesh)}, meshHasUV);
+        w.f32("corner_n", {uint32_t(cornerN.size() / 3), 3}, cornerN);
+        w.f32("corner_uv", {uint32_t(cornerUV.size() / 2), 2}, cornerUV);
+    }
     if (!patchIdx.empty()) {
         // mesh_kind 1 = bilinear patch mesh: its mesh_ntris patches take 4 indices each (p00 p10 p01 p11) from patch_indices
         w.u32("mesh_kind", {uint32_t(nMesh)}, meshKind);

@@ -23,7 +23,7 @@ struct b200pt_render {
     RenderSceneDev dev{};
     void *dSpectra = nullptr, *dMaterials = nullptr, *dLights = nullptr, *dMeshes = nullptr;
     void *dLightBvh = nullptr, *dBitTrails = nullptr, *dInfinite = nullptr;
-    void *dLens = nullptr, *dPupil = nullptr;
+    void *dLens = nullptr, *dPupil = nullptr, *dCornerAttr = nullptr;
     void *dMedia = nullptr;
     std::vector<void *> dGrids;  // density and majorant grids of the media
     double *dFilm = nullptr;
@@ -72,6 +72,7 @@ int b200pt_render_destroy(b200pt_render *r) {
     cudaFree(r->dMedia);
     for (void *g : r->dGrids) cudaFree(g);
     cudaFree(r->dPupil);
+    cudaFree(r->dCornerAttr);
     cudaFree(r->dFilm);
     cudaFree(r->dImage);
     cudaFree(r->dPaths);
@@ -107,7 +108,7 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         (rc = Upload(ctx, r->host.lightBvhNodes, &r->dLightBvh)) ||
         (rc = Upload(ctx, r->host.lightBitTrails, &r->dBitTrails)) ||
         (rc = Upload(ctx, r->host.infiniteLights, &r->dInfinite)) || (rc = Upload(ctx, r->host.lens, &r->dLens)) ||
-        (rc = Upload(ctx, r->host.pupilBounds, &r->dPupil)))
+        (rc = Upload(ctx, r->host.pupilBounds, &r->dPupil)) || (rc = Upload(ctx, r->host.cornerAttr, &r->dCornerAttr)))
         return fail(rc);
     for (size_t i = 0; i < r->host.media.size(); ++i) {  // grids first: the medium table points at them
         if (r->host.media[i].type != 1) continue;
@@ -132,6 +133,7 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     r->dev.infiniteLights = (const int32_t *)r->dInfinite;
     r->dev.camera.lens = (const float *)r->dLens;
     r->dev.camera.pupilBounds = (const float *)r->dPupil;
+    r->dev.cornerAttr = (const float *)r->dCornerAttr;
     r->dev.prims = scene->dev.prims;
     r->dev.instances = scene->dev.instances;
     for (const MaterialDev &m : r->host.materials) r->matMask |= 1u << m.type;

@@ -177,6 +177,13 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     std::map<uint64_t, uint32_t> slotOf;
     for (uint32_t s = 0; s < hs.prims.size(); ++s)
         if (hs.prims[s].mesh < kInstanceTag) slotOf[(uint64_t(hs.prims[s].mesh) << 32) | hs.prims[s].tri] = s;
+    // triangles per mesh, for the per-corner attribute arrays
+    std::vector<uint32_t> meshTris(d->n_meshes, 0), meshKind(d->n_meshes, 0);
+    for (const PrimSlot &ps : hs.prims)
+        if (ps.mesh < d->n_meshes) {
+            meshTris[ps.mesh] = std::max(meshTris[ps.mesh], ps.tri + 1);
+            meshKind[ps.mesh] = ps.kind;
+        }
     out.meshes.resize(d->n_meshes);
     for (uint32_t i = 0; i < d->n_meshes; ++i) {
         const b200pt_mesh_attr &m = d->meshes[i];
@@ -189,7 +196,19 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
             if (mi < -1 || mo < -1 || mi >= int32_t(d->n_media) || mo >= int32_t(d->n_media))
                 return bad("mesh medium index out of range");
         }
-        out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, 0, mi, mo};
+        uint32_t nOff = kNoCornerAttr, uvOff = kNoCornerAttr;
+        if (meshKind[i] == 0 && (m.corner_n || m.corner_uv)) {
+            if (out.cornerAttr.size() + 15 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
+            if (m.corner_n) {
+                nOff = uint32_t(out.cornerAttr.size());
+                out.cornerAttr.insert(out.cornerAttr.end(), m.corner_n, m.corner_n + 9 * size_t(meshTris[i]));
+            }
+            if (m.corner_uv) {
+                uvOff = uint32_t(out.cornerAttr.size());
+                out.cornerAttr.insert(out.cornerAttr.end(), m.corner_uv, m.corner_uv + 6 * size_t(meshTris[i]));
+            }
+        }
+        out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, nOff, mi, mo, uvOff, 0};
     }
     out.lights.resize(d->n_lights);
     for (uint32_t i = 0; i < d->n_lights; ++i) {

@@ -22,6 +22,7 @@ struct RenderHost {
     std::vector<int32_t> infiniteLights;   // light indices
     std::vector<MediumDev> media;          // density / majorants pointers are filled by the owner of the grids
     std::vector<std::pair<std::vector<float>, std::vector<float>>> mediumGrids;  // per medium: density, majorants
+    std::vector<float> cornerAttr;         // per-corner normals / uv (MeshAttrDev::nOff, uvOff)
     std::vector<float> lens, pupilBounds;  // realistic camera: 4 floats per element / per film-radius bin
     int width = 0, height = 0;
 };

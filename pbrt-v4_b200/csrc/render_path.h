@@ -296,10 +296,10 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
         V3 dInst = mk(mi[0] * p.rayD.x + mi[1] * p.rayD.y + mi[2] * p.rayD.z,
                       mi[4] * p.rayD.x + mi[5] * p.rayD.y + mi[6] * p.rayD.z,
                       mi[8] * p.rayD.x + mi[9] * p.rayD.y + mi[10] * p.rayD.z);
-        si = SlotInteraction(tv, b0, b1, b2, -dInst, mesh.flipNormal != 0);
+        si = SlotInteraction(rs.prims, slot, tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
         TransformSurfHit(in, si);
     } else {
-        si = SlotInteraction(tv, b0, b1, b2, wo, mesh.flipNormal != 0);
+        si = SlotInteraction(rs.prims, slot, tv, b0, b1, b2, wo, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
     }
 
     // ---- emitted light at the hit (cpu/integrators.cpp:664-679)
@@ -321,7 +321,7 @@ B2_SPECTRAL_LOOP
                     float pmf = al.aliasP;
                     if (rs.integrator.lightSampler == 0) pmf = 1.f / rs.nLights;
                     if (lightBvh) pmf = LightBvhPMF(rs, Mid(p.prev.pi), p.prev.ns, mesh.lightFirst + (int)tv.tri);
-                    float p_l = pmf * ShapePDF(tv, p.prev, p.rayD, al.flipNormal != 0);
+                    float p_l = pmf * ShapePDF(rs.prims, slot, tv, p.prev, p.rayD, al.flipNormal != 0);
                     for (int k = 0; k < kNLambda; ++k) io.SetRl(k, io.Rl(k) * p_l);
                     avg = AvgRuRl(io);
                 }
@@ -339,7 +339,7 @@ B2_SPECTRAL_LOOP
                 if (rs.integrator.lightSampler == 0) pmf = 1.f / rs.nLights;
                 if (lightBvh)
                     pmf = LightBvhPMF(rs, Mid(p.prev.pi), p.prev.ns, mesh.lightFirst + (int)tv.tri);
-                float p_l = pmf * ShapePDF(tv, p.prev, p.rayD, al.flipNormal != 0);
+                float p_l = pmf * ShapePDF(rs.prims, slot, tv, p.prev, p.rayD, al.flipNormal != 0);
                 w = PowerHeuristic(p.pB, p_l);
             }
             const SpectrumTable &sp = rs.spectra[al.spectrum];
@@ -427,7 +427,7 @@ B2_SPECTRAL_LOOP
             ss.ok = false;
             if (lidx >= 0 && light.type == 0) {
                 TriVerts lt = LoadTri(rs.prims, light.slot);
-                ss = SampleShapeSolidAngle(lt, ctx, uLight0, uLight1, light.flipNormal != 0);
+                ss = SampleShapeSolidAngle(rs.prims, light.slot, lt, ctx, uLight0, uLight1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri).n);
             }
             V3 cp = Mid(ctx.pi);
             if (ss.ok && ss.pdf != 0 && LengthSquared(Mid(ss.pi) - cp) != 0) {

@@ -6,16 +6,27 @@ namespace b200pt {
 
 struct TriVerts {
     V3 p0, p1, p2;
-    V3 p3;  // bilinear patch: p00 p10 p01 p11 in p0..p3 (the mesh's index order)
-    uint32_t mesh, tri, kind;
+    uint32_t mesh, tri, kind;  // kind 1: a bilinear patch; its code loads the four corners itself (PatchVerts)
 };
+// bilinear patch: p00 p10 p01 p11 in p0..p3 (the mesh's index order)
+struct PatchVerts {
+    V3 p0, p1, p2, p3;
+};
+B2_HD PatchVerts LoadPatch(const void *prims, uint32_t slot) {
+    const PrimSlot *s = reinterpret_cast<const PrimSlot *>(prims) + slot;
+    PatchVerts t;
+    t.p0 = mk(s->p0[0], s->p0[1], s->p0[2]);
+    t.p1 = mk(s->p1[0], s->p1[1], s->p1[2]);
+    t.p2 = mk(s->p2[0], s->p2[1], s->p2[2]);
+    t.p3 = mk(s->p3[0], s->p3[1], s->p3[2]);
+    return t;
+}
 B2_HD TriVerts LoadTri(const void *prims, uint32_t slot) {
     const PrimSlot *s = reinterpret_cast<const PrimSlot *>(prims) + slot;
     TriVerts t;
     t.p0 = mk(s->p0[0], s->p0[1], s->p0[2]);
     t.p1 = mk(s->p1[0], s->p1[1], s->p1[2]);
     t.p2 = mk(s->p2[0], s->p2[1], s->p2[2]);
-    t.p3 = mk(s->p3[0], s->p3[1], s->p3[2]);
     t.mesh = s->mesh;
     t.tri = s->tri;
     t.kind = s->kind;
@@ -29,11 +40,43 @@ struct SurfHit {
     float u, v;
 };
 
-// Triangle::InteractionFromIntersection (shapes.h:884-1010) for meshes without per-vertex n/s/uv:
-// default uv (0,0),(1,0),(1,1); dpdu/dpdv from the uv determinant; n = normalized cross(dp02, dp12).
-B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b2, V3 wo, bool flipNormal) {
+// per-corner normals / uv of triangle `tri` of a mesh, null where the mesh has none (MeshAttrDev::nOff, uvOff)
+struct CornerAttr {
+    const float *n, *uv;
+};
+B2_HD CornerAttr CornersOf(const RenderSceneDev &rs, const MeshAttrDev &mesh, uint32_t tri) {
+    CornerAttr c;
+    c.n = mesh.nOff != kNoCornerAttr ? rs.cornerAttr + mesh.nOff + 9 * size_t(tri) : nullptr;
+    c.uv = mesh.uvOff != kNoCornerAttr ? rs.cornerAttr + mesh.uvOff + 6 * size_t(tri) : nullptr;
+    return c;
+}
+
+// The `if (mesh->n || mesh->s)` block of Triangle::InteractionFromIntersection (shapes.h:934-1005) without
+// per-vertex tangents: interpolated shading normal, tangent = dpdu made orthogonal to it, and
+// SetShadingGeometry(..., orientationIsAuthoritative = true) (interaction.h:194-211): the geometric normal follows ns.
+B2_HD_NOINLINE void TriangleShadingNormal(SurfHit &h, const float *cn, float b0, float b1, float b2, V3 dpdu) {
+    V3 n0 = mk(cn[0], cn[1], cn[2]), n1 = mk(cn[3], cn[4], cn[5]), n2 = mk(cn[6], cn[7], cn[8]);
+    V3 ns = b0 * n0 + b1 * n1 + b2 * n2;
+    ns = LengthSquared(ns) > 0 ? Normalize(ns) : h.n;
+    V3 ss = dpdu;
+    V3 ts = Cross(ns, ss);
+    if (LengthSquared(ts) > 0)
+        ss = Cross(ts, ns);
+    else
+        CoordinateSystem(ns, &ss, &ts);
+    h.ns = ns;
+    h.n = FaceForward(h.n, ns);
+    h.dpdus = ss;
+}
+
+// Triangle::InteractionFromIntersection (shapes.h:884-1010); without per-vertex uv the corners get
+// (0,0),(1,0),(1,1); dpdu/dpdv from the uv determinant; n = normalized cross(dp02, dp12).
+B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b2, V3 wo, bool flipNormal,
+                                  CornerAttr ca = CornerAttr{nullptr, nullptr}) {
     SurfHit h;
-    const float uv[3][2] = {{0, 0}, {1, 0}, {1, 1}};
+    float uv[3][2] = {{0, 0}, {1, 0}, {1, 1}};
+    if (ca.uv)
+        for (int k = 0; k < 6; ++k) uv[k >> 1][k & 1] = ca.uv[k];
     float duv02x = uv[0][0] - uv[2][0], duv02y = uv[0][1] - uv[2][1];
     float duv12x = uv[1][0] - uv[2][0], duv12y = uv[1][1] - uv[2][1];
     V3 dp02 = t.p0 - t.p2, dp12 = t.p1 - t.p2;
@@ -63,12 +106,13 @@ B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b
     h.ns = n;
     h.dpdus = dpdu;
     h.wo = Normalize(wo);  // Interaction constructor (interaction.h:36-41)
+    if (ca.n) TriangleShadingNormal(h, ca.n, b0, b1, b2, dpdu);
     return h;
 }
 
 // BilinearPatch::InteractionFromIntersection (shapes.h:1396-1500) for meshes without per-vertex uv / n: the point and
 // both partial derivatives are lerps of the four corners at the hit's (u,v); the normal is their cross product.
-B2_HD_CALL SurfHit PatchInteraction(const TriVerts &t, float u, float v, V3 wo, bool flipNormal) {
+B2_HD_CALL SurfHit PatchInteraction(const PatchVerts &t, float u, float v, V3 wo, bool flipNormal) {
     SurfHit h;
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     V3 e0 = (1 - v) * p00 + v * p01, e1 = (1 - v) * p10 + v * p11;
@@ -89,9 +133,13 @@ B2_HD_CALL SurfHit PatchInteraction(const TriVerts &t, float u, float v, V3 wo, 
 }
 
 // Shape::Intersect's interaction for either kind of slot; (b1, b2) of a patch record are its (u, v)
-B2_HD SurfHit SlotInteraction(const TriVerts &t, float b0, float b1, float b2, V3 wo, bool flipNormal) {
-    if (t.kind == 1) return PatchInteraction(t, b1, b2, wo, flipNormal);
-    return TriangleInteraction(t, b0, b1, b2, wo, flipNormal);
+B2_HD SurfHit SlotInteraction(const void *prims, uint32_t slot, const TriVerts &t, float b0, float b1, float b2, V3 wo,
+                              bool flipNormal, CornerAttr ca) {
+    if (t.kind == 1) {
+        const PatchVerts pv = LoadPatch(prims, slot);
+        return PatchInteraction(pv, b1, b2, wo, flipNormal);
+    }
+    return TriangleInteraction(t, b0, b1, b2, wo, flipNormal, ca);
 }
 
 // Transform::operator()(SurfaceInteraction) for an object instance (util/transform.cpp:227-258,
@@ -157,13 +205,23 @@ struct ShapeSampleOut {
 B2_HD float TriArea(const TriVerts &t) { return 0.5f * Length(Cross(t.p1 - t.p0, t.p2 - t.p0)); }  // shapes.h:866-871
 
 // Triangle::Sample(u) by area (shapes.h:1012-1047)
-B2_HD ShapeSampleOut SampleTriangleArea(const TriVerts &t, float u0, float u1, bool flipNormal) {
+// the sampled point's normal: towards the interpolated vertex normal where the mesh has normals (shapes.h:1024-1029, 1112-1117)
+B2_HD V3 SampledTriangleNormal(const TriVerts &t, const float b[3], bool flipNormal, const float *cn) {
+    V3 n = Normalize(Cross(t.p1 - t.p0, t.p2 - t.p0));
+    if (cn) {
+        V3 ns = b[0] * mk(cn[0], cn[1], cn[2]) + b[1] * mk(cn[3], cn[4], cn[5]) + (1 - b[0] - b[1]) * mk(cn[6], cn[7], cn[8]);
+        n = FaceForward(n, ns);
+    } else if (flipNormal)
+        n = n * -1.f;
+    return n;
+}
+
+B2_HD ShapeSampleOut SampleTriangleArea(const TriVerts &t, float u0, float u1, bool flipNormal, const float *cn = nullptr) {
     ShapeSampleOut o;
     float b[3];
     SampleUniformTriangle(u0, u1, b);
     V3 p = b[0] * t.p0 + b[1] * t.p1 + b[2] * t.p2;
-    V3 n = Normalize(Cross(t.p1 - t.p0, t.p2 - t.p0));
-    if (flipNormal) n = n * -1.f;
+    V3 n = SampledTriangleNormal(t, b, flipNormal, cn);
     V3 pAbsSum = Abs(b[0] * t.p0) + Abs(b[1] * t.p1) + Abs((1 - b[0] - b[1]) * t.p2);
     V3 pError = GammaF(6) * pAbsSum;
     o.pi = MakeP3i(p, pError);
@@ -272,13 +330,13 @@ B2_HD void CosWarpWeights(const TriVerts &t, V3 rp, V3 ns, float w[4]) {  // sha
 
 // Triangle::Sample(ctx, u) (shapes.h:1052-1130)
 B2_HD ShapeSampleOut SampleTriangleSolidAngle(const TriVerts &t, const LightCtx &ctx, float u0, float u1,
-                                              bool flipNormal) {
+                                              bool flipNormal, const float *cn = nullptr) {
     ShapeSampleOut o;
     o.ok = false;
     V3 rp = Mid(ctx.pi);
     float solidAngle = SphericalTriangleArea(Normalize(t.p0 - rp), Normalize(t.p1 - rp), Normalize(t.p2 - rp));
     if (solidAngle < kMinSphericalSampleArea || solidAngle > kMaxSphericalSampleArea) {
-        o = SampleTriangleArea(t, u0, u1, flipNormal);
+        o = SampleTriangleArea(t, u0, u1, flipNormal, cn);
         V3 wi = Mid(o.pi) - rp;
         if (LengthSquared(wi) == 0) {
             o.ok = false;
@@ -305,8 +363,7 @@ B2_HD ShapeSampleOut SampleTriangleSolidAngle(const TriVerts &t, const LightCtx 
     V3 pAbsSum = Abs(b[0] * t.p0) + Abs(b[1] * t.p1) + Abs((1 - b[0] - b[1]) * t.p2);
     V3 pError = GammaF(6) * pAbsSum;
     V3 p = b[0] * t.p0 + b[1] * t.p1 + b[2] * t.p2;
-    V3 n = Normalize(Cross(t.p1 - t.p0, t.p2 - t.p0));
-    if (flipNormal) n = n * -1.f;
+    V3 n = SampledTriangleNormal(t, b, flipNormal, cn);
     o.pi = MakeP3i(p, pError);
     o.n = n;
     o.pdf = pdf;
@@ -317,7 +374,7 @@ B2_HD ShapeSampleOut SampleTriangleSolidAngle(const TriVerts &t, const LightCtx 
 // ---- emissive bilinear patches: BilinearPatch::Sample / PDF (shapes.cpp:1158-1372)
 
 // BilinearPatch::IsRectangle (shapes.h:1510-1532)
-B2_HD bool PatchIsRectangle(const TriVerts &t) {
+B2_HD bool PatchIsRectangle(const PatchVerts &t) {
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     auto same = [](V3 a, V3 b) { return a.x == b.x && a.y == b.y && a.z == b.z; };
     if (same(p00, p01) || same(p01, p11) || same(p11, p10) || same(p10, p00)) return false;
@@ -439,7 +496,7 @@ B2_HD void InvertSphericalRectangleSample(V3 pRef, V3 s, V3 ex, V3 ey, V3 pRect,
 }
 
 // the corner weights of approximately uniform area sampling (shapes.cpp:1172-1175, 1241-1244)
-B2_HD void PatchAreaWeights(const TriVerts &t, float w[4]) {
+B2_HD void PatchAreaWeights(const PatchVerts &t, float w[4]) {
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     w[0] = Length(Cross(p10 - p00, p01 - p00));
     w[1] = Length(Cross(p10 - p00, p11 - p10));
@@ -448,7 +505,7 @@ B2_HD void PatchAreaWeights(const TriVerts &t, float w[4]) {
 }
 
 // BilinearPatch::Sample(u) by area (shapes.cpp:1158-1217), no image distribution, no per-vertex uv / n
-B2_HD ShapeSampleOut SamplePatchArea(const TriVerts &t, bool rectangle, float u0, float u1, bool flipNormal) {
+B2_HD ShapeSampleOut SamplePatchArea(const PatchVerts &t, bool rectangle, float u0, float u1, bool flipNormal) {
     ShapeSampleOut o;
     o.ok = false;
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
@@ -484,7 +541,7 @@ B2_HD void PatchCosWeights(V3 v00, V3 v10, V3 v01, V3 v11, V3 ns, float w[4]) { 
 constexpr float kPatchMinSphericalSampleArea = 1e-4f;  // shapes.h:1538
 
 // BilinearPatch::Sample(ctx, u) (shapes.cpp:1257-1330)
-B2_HD_CALL ShapeSampleOut SamplePatchSolidAngle(const TriVerts &t, const LightCtx &ctx, float u0, float u1, bool flipNormal) {
+B2_HD_CALL ShapeSampleOut SamplePatchSolidAngle(const PatchVerts &t, const LightCtx &ctx, float u0, float u1, bool flipNormal) {
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     V3 rp = Mid(ctx.pi);
     V3 v00 = Normalize(p00 - rp), v10 = Normalize(p10 - rp), v01 = Normalize(p01 - rp), v11 = Normalize(p11 - rp);
@@ -526,7 +583,7 @@ B2_HD_CALL ShapeSampleOut SamplePatchSolidAngle(const TriVerts &t, const LightCt
 }
 
 // BilinearPatch::PDF(ctx, wi) (shapes.cpp:1332-1372) with PDF(intr) (:1219-1255)
-B2_HD_CALL float PatchPDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
+B2_HD_CALL float PatchPDF(const PatchVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     V3 rp = Mid(ctx.pi);
     V3 o = OffsetRayOrigin(ctx.pi, ctx.n, wi);
@@ -601,12 +658,19 @@ B2_HD float TrianglePDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flip
 
 
 // Shape::Sample(ctx, u) / Shape::PDF(ctx, wi) of the emitter in slot `t`
-B2_HD ShapeSampleOut SampleShapeSolidAngle(const TriVerts &t, const LightCtx &ctx, float u0, float u1, bool flipNormal) {
-    if (t.kind == 1) return SamplePatchSolidAngle(t, ctx, u0, u1, flipNormal);
-    return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal);
+B2_HD ShapeSampleOut SampleShapeSolidAngle(const void *prims, uint32_t slot, const TriVerts &t, const LightCtx &ctx, float u0,
+                                           float u1, bool flipNormal, const float *cn) {
+    if (t.kind == 1) {
+        const PatchVerts pv = LoadPatch(prims, slot);
+        return SamplePatchSolidAngle(pv, ctx, u0, u1, flipNormal);
+    }
+    return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal, cn);
 }
-B2_HD float ShapePDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
-    if (t.kind == 1) return PatchPDF(t, ctx, wi, flipNormal);
+B2_HD float ShapePDF(const void *prims, uint32_t slot, const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
+    if (t.kind == 1) {
+        const PatchVerts pv = LoadPatch(prims, slot);
+        return PatchPDF(pv, ctx, wi, flipNormal);
+    }
     return TrianglePDF(t, ctx, wi, flipNormal);
 }
 }  // namespace b200pt

@@ -48,9 +48,12 @@ struct MeshAttrDev {
     int32_t material;
     int32_t lightFirst;  // light index of triangle 0 of this mesh, -1 if not emissive
     uint32_t flipNormal;
-    uint32_t pad;
+    uint32_t nOff;  // per-corner normals of triangle t at cornerAttr[nOff + 9 t], kNoCornerAttr = none
     int32_t mediumInside, mediumOutside;  // MediumInterface; equal = no transition (the ray keeps its medium)
+    uint32_t uvOff;  // per-corner uv of triangle t at cornerAttr[uvOff + 6 t], kNoCornerAttr = none
+    uint32_t pad;
 };
+constexpr uint32_t kNoCornerAttr = 0xFFFFFFFFu;
 
 // One participating medium (media.h:217-345): homogeneous, or a density grid with its majorant grid.
 struct MediumDev {
@@ -130,6 +133,7 @@ struct RenderSceneDev {
     float lightBvhBounds[6];
     const MediumDev *media;
     uint32_t nMedia;
+    const float *cornerAttr;  // per-corner normals / uv of the meshes that have them (MeshAttrDev::nOff, uvOff)
 };
 
 // Per-path state, structure of arrays over `n` paths of a pass.  Spectral arrays are [k][path].

@@ -108,9 +108,24 @@ class RenderScene:
                                    float(lf[1]), float(lf[2]), float(lf[3]), float(lf[4]), float(lf[5]), int(li[4]),
                                    ltype)
         meshes = (capi.MeshAttr * max(nme, 1))()
+        # per-corner normals / uv: the meshes that have them take their 3 * ntris rows from corner_n / corner_uv in order
+        has_n = d["mesh_has_n"] if "mesh_has_n" in d else np.zeros(nme, np.uint32)
+        has_uv = d["mesh_has_uv"] if "mesh_has_uv" in d else np.zeros(nme, np.uint32)
+        ntris = d["mesh_ntris"].astype(np.int64)
+        n_at = uv_at = 0
         for i in range(nme):
             a = d["mesh_attr"][i]
             meshes[i] = capi.MeshAttr(int(a[0]), int(a[1]), int(max(a[2], 0)))
+            if has_n[i]:
+                cn = np.ascontiguousarray(d["corner_n"][n_at:n_at + 3 * ntris[i]], np.float32)
+                n_at += 3 * int(ntris[i])
+                meshes[i].corner_n = capi.fptr(cn)
+                keep.append(cn)
+            if has_uv[i]:
+                cuv = np.ascontiguousarray(d["corner_uv"][uv_at:uv_at + 3 * ntris[i]], np.float32)
+                uv_at += 3 * int(ntris[i])
+                meshes[i].corner_uv = capi.fptr(cuv)
+                keep.append(cuv)
         r.n_spectra, r.n_materials, r.n_lights, r.n_meshes = ns, nm, nl, nme
         r.spectra, r.materials, r.lights, r.meshes = spectra, mats, lights, meshes
         keep += [spectra, mats, lights, meshes]

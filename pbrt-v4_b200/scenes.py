@@ -341,7 +341,7 @@ MATERIALS = {
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
                  boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
-                 film="rgb", nbuckets=31, patches=False):
+                 film="rgb", nbuckets=31, patches=False, smooth=False):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -429,6 +429,39 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
                   'AttributeBegin', '  ' + MATERIALS["conductor_rough"], '  ReverseOrientation',
                   '  ' + sheet(0.05, 0.3, 0.1, 0.45, 1, lambda u, v: 0.75 + 0.18 * (2 * u - 1) * (2 * v - 1)),
                   'AttributeEnd']
+    if smooth:
+        # triangle meshes with per-vertex normals and uv (Triangle::InteractionFromIntersection's shading geometry,
+        # shapes.h:934-1005): an anisotropic metal ball, a diffuse ball with normals only, and a small emissive
+        # dome whose normals decide its emitting side (Triangle::Sample's FaceForward(n, ns), shapes.h:1024-1029)
+        def ball(c, r, nu, nv, vmax=np.pi, with_uv=True, inward=False):
+            th = np.linspace(0.0, vmax, nv + 1)
+            ph = np.linspace(0.0, 2 * np.pi, nu + 1)
+            nrm = np.array([[np.sin(t) * np.cos(f), np.cos(t), np.sin(t) * np.sin(f)] for t in th for f in ph])
+            pts = np.asarray(c) + r * nrm
+            uv = np.array([[f / (2 * np.pi), t / np.pi] for t in th for f in ph])
+            idx = []
+            for j in range(nv):
+                for i in range(nu):
+                    a, b = j * (nu + 1) + i, (j + 1) * (nu + 1) + i
+                    if j > 0:
+                        idx += [a, a + 1, b]
+                    if j < nv - 1 or vmax < np.pi:
+                        idx += [a + 1, b + 1, b]
+            if inward:
+                nrm = -nrm
+            txt = (f'Shape "trianglemesh" "integer indices" [{" ".join(map(str, idx))}] "point3 P" '
+                   f'[{" ".join(f"{float(x):.7g}" for x in pts.reshape(-1))}] "normal N" '
+                   f'[{" ".join(f"{float(x):.7g}" for x in nrm.reshape(-1))}]')
+            if with_uv:
+                txt += f' "point2 uv" [{" ".join(f"{float(x):.7g}" for x in uv.reshape(-1))}]'
+            return txt
+        lines += ['AttributeBegin', '  ' + MATERIALS["conductor_reflectance"], '  ' + ball((0.68, 0.5, 0.3), 0.16, 12, 8),
+                  'AttributeEnd',
+                  'AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.3 0.6 0.7]',
+                  '  ' + ball((0.25, 0.78, 0.35), 0.13, 10, 6, with_uv=False), 'AttributeEnd',
+                  'AttributeBegin', '  AreaLightSource "diffuse" "rgb L" [4 5 9]',
+                  '  Material "diffuse" "rgb reflectance" [0 0 0]',
+                  '  ' + ball((0.15, 0.05, 0.2), 0.1, 8, 3, vmax=0.5 * np.pi, with_uv=False), 'AttributeEnd']
     if infinite is not None:
         lines.append(f'LightSource "infinite" "rgb L" [{infinite[0]} {infinite[1]} {infinite[2]}]')
     with open(path, "w") as f:

@@ -130,6 +130,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
     rs.camera.pupilBounds = rh.pupilBounds.data();
+    rs.cornerAttr = rh.cornerAttr.data();
     for (size_t i = 0; i < rh.media.size(); ++i) {
         rh.media[i].density = rh.mediumGrids[i].first.data();
         rh.media[i].majorants = rh.mediumGrids[i].second.data();
@@ -188,6 +189,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
     rs.camera.pupilBounds = rh.pupilBounds.data();
+    rs.cornerAttr = rh.cornerAttr.data();
     for (size_t i = 0; i < rh.media.size(); ++i) {
         rh.media[i].density = rh.mediumGrids[i].first.data();
         rh.media[i].majorants = rh.mediumGrids[i].second.data();

@@ -36,7 +36,8 @@ def _check(P, rendercheck, name, **kw):
 @pytest.mark.parametrize("name", ["cornell_r64_s16", "cornell_r48_s8_uniform", "cornell_metal_r64_s16",
                                   "cornell_metal2_r48_s8", "cornell_instanced_r64_s16", "cornell_manylights_r64_s16",
                                   "cornell_infinite_r64_s16", "cornell_infinite_power_r48_s8",
-                                  "cornell_patches_r64_s16", "cornell_patchlights_r64_s16"])  # + bilinear patches, shaded and emissive
+                                  "cornell_patches_r64_s16", "cornell_patchlights_r64_s16",  # bilinear patches, shaded and emissive
+                                  "cornell_smooth_r64_s16"])  # per-vertex normals + uv (shading geometry)
 def test_golden_image(P, rendercheck, name):
     _check(P, rendercheck, name)
 
