@@ -305,6 +305,12 @@ typedef struct b200pt_render_desc {
     const struct b200pt_medium *media;
     const int32_t *mesh_media;
     int32_t camera_medium;
+    /* camera_type 2 = the ISET OmniCamera without a microlens array (cameras.cpp:2823-2989 TraceElement /
+     * TraceLensesFromFilm, :3118-3138 SampleExitPupil, :3329-3373 GenerateRay): the camera_type 1 tables (from
+     * OmniCamera's own constructor) plus lens_element_transforms = n x {transform[16], inverse[16]} row major, the
+     * LensElementInterface::transform of each interface (cameras.h:856-878; decentred / tilted elements), NULL =
+     * all identity. */
+    const float *lens_element_transforms;
 } b200pt_render_desc;
 
 typedef struct b200pt_render b200pt_render;

@@ -294,8 +294,41 @@ int main(int argc, char **argv) {
         w.f32("camera_exit_pupil", {uint32_t(pupil.size() / 4), 4}, pupil);
         const Bounds2f &pe = rc->physicalExtent;
         w.f32("camera_extent", {5}, {pe.pMin.x, pe.pMin.y, pe.pMax.x, pe.pMax.y, film.Diagonal()});
+    } else if (camera.Is<OmniCamera>()) {
+        // ISET OmniCamera without a microlens array (cameras.h:856-1040): the RealisticCamera tables plus one
+        // rigid transform per element interface and the chromatic-aberration switch
+        const OmniCamera *oc = camera.Cast<OmniCamera>();
+        if (oc->apertureImage) die("aperture images are not dumped");
+        if (oc->microlens.elementInterfaces.size() > 0) die("microlens arrays are not dumped");
+        w.u32("camera_type", {1}, {2});
+        w.f32("render_from_camera", {16}, Mat(oc->cameraTransform.renderFromCamera.startTransform.GetMatrix()));
+        std::vector<float> lens, pupil, xf;
+        for (const auto &e : oc->elementInterfaces) {
+            if (e.asphericCoefficients.size() > 0) die("aspheric elements are not dumped (the reference skips them too)");
+            lens.insert(lens.end(), {e.curvatureRadius.x, e.thickness, e.eta, e.apertureRadius.x});
+            std::vector<float> m = Mat(e.transform.GetMatrix()), mi = Mat(e.transform.GetInverseMatrix());
+            xf.insert(xf.end(), m.begin(), m.end());
+            xf.insert(xf.end(), mi.begin(), mi.end());
+        }
+        for (const Bounds2f &b : oc->exitPupilBounds) pupil.insert(pupil.end(), {b.pMin.x, b.pMin.y, b.pMax.x, b.pMax.y});
+        w.f32("camera_lens", {uint32_t(lens.size() / 4), 4}, lens);
+        w.f32("camera_lens_transforms", {uint32_t(xf.size() / 32), 32}, xf);
+        w.f32("camera_exit_pupil", {uint32_t(pupil.size() / 4), 4}, pupil);
+        const Bounds2f &pe = oc->physicalExtent;
+        w.f32("camera_extent", {5}, {pe.pMin.x, pe.pMin.y, pe.pMax.x, pe.pMax.y, film.Diagonal()});
+        w.u32("camera_flags", {1}, {oc->caFlag ? 1u : 0u});
+        if (getenv("DUMPSCENE_CAMDEBUG")) {
+            fprintf(stderr, "omni: back thickness %g rearZ %g pupil[0] %g %g %g %g\n", oc->elementInterfaces.back().thickness,
+                    oc->LensRearZ(), pupil[0], pupil[1], pupil[2], pupil[3]);
+            CameraSample cs;
+            cs.pFilm = Point2f(film.FullResolution().x / 2 + 0.5f, film.FullResolution().y / 2 + 0.5f);
+            cs.pLens = Point2f(0.5f, 0.5f);
+            SampledWavelengths lam = SampledWavelengths::SampleUniform(0.5f);
+            auto cr = oc->GenerateRay(cs, lam);
+            fprintf(stderr, "omni: centre ray %s\n", cr ? "ok" : "vignetted");
+        }
     } else
-        die("only the perspective and realistic cameras are dumped so far");
+        die("only the perspective, realistic and omni cameras are dumped so far");
 
     // ---- film (RGBFilm) and its sensor
     auto dumpFilm = [&](const auto *rf) {
@@ -567,6 +600,7 @@ int main(int argc, char **argv) {
             }
         w.i32("mesh_media", {uint32_t(nMesh), 2}, mm);
         Medium camMedium = camera.Is<PerspectiveCamera>() ? camera.Cast<PerspectiveCamera>()->medium
+                           : camera.Is<OmniCamera>()      ? camera.Cast<OmniCamera>()->medium
                                                           : camera.Cast<RealisticCamera>()->medium;
         w.i32("camera_medium", {1}, {mediumIndex(camMedium)});
         // media_i: {type, sigma_a, sigma_s, nx, ny, nz, mres[3]}; media_f: {g, bounds[6], mediumFromRender[16],

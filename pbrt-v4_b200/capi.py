@@ -164,7 +164,8 @@ class RenderDesc(C.Structure):
                 ("n_exit_pupil_bounds", C.c_uint32), ("exit_pupil_bounds", C.POINTER(C.c_float)),
                 ("physical_extent", C.c_float * 4), ("film_diagonal", C.c_float),
                 ("integrator_type", C.c_uint32), ("n_media", C.c_uint32), ("media", C.POINTER(Medium)),
-                ("mesh_media", C.POINTER(C.c_int32)), ("camera_medium", C.c_int32)]
+                ("mesh_media", C.POINTER(C.c_int32)), ("camera_medium", C.c_int32),
+                ("lens_element_transforms", C.POINTER(C.c_float))]
 
 
 class RenderStats(C.Structure):

@@ -287,7 +287,7 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
 #define B2_SHADE_MIN_BLOCKS 4  // 128 registers: the layered walks are latency bound, four blocks per SM beat three
 #endif
 // ---- one path vertex: PathIntegrator::Li loop body (cpu/integrators.cpp:640-760)
-template <int MAT, int LBVH, int VOL>
+template <int MAT, int LBVH, int VOL, int EXT>
 __global__ void __launch_bounds__(kShadeBlock, B2_SHADE_MIN_BLOCKS)
 ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -316,7 +316,7 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     uint2 h0 = h[0], h1 = h[1], h2 = h[2];
     hit[0] = h0.x; hit[1] = h0.y; hit[2] = h1.x; hit[3] = h1.y; hit[4] = h2.x; hit[5] = h2.y;
     DevIO io(pb, path, counts + 1, myBeta);
-    ShadeVertex<DevIO, MAT, LBVH, VOL>(rs, p, hit, io);
+    ShadeVertex<DevIO, MAT, LBVH, VOL, EXT>(rs, p, hit, io);
     if (p.flags & PF_ALIVE) {
         int *next = pb.counts + kCountStride * (depth + 1);
         int slot = QueuePush(next);
@@ -363,7 +363,7 @@ VolSortKernel(RenderSceneDev rs, PassBuffers pb, int depth, int mode) {
 #ifndef B2_VOL_MIN_BLOCKS
 #define B2_VOL_MIN_BLOCKS 3
 #endif
-template <int LBVH>
+template <int LBVH, int EXT>
 __global__ void __launch_bounds__(kShadeBlock, B2_VOL_MIN_BLOCKS)
 VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width, int kind) {
     int qi = blockIdx.x * blockDim.x + threadIdx.x;
@@ -393,7 +393,7 @@ VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int w
         mine[(2 * kNLambda + k) * kShadeBlock] = pb.rl[k * n + path];
     }
     MediumIO io(pb, path, counts + 1, mine);
-    int res = VolMediumStep<MediumIO, LBVH>(rs, p, tHit, io);
+    int res = VolMediumStep<MediumIO, LBVH, EXT>(rs, p, tHit, io);
     if (res != VOL_TERMINATED) {
 #pragma unroll 8
         for (int k = 0; k < kNLambda; ++k) {
@@ -421,6 +421,7 @@ VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int w
 // ---- volpath: one segment of every light sample's transmittance walk (cpu/integrators.cpp:1334-1395).  pb.shHits
 // holds the closest hits of the shadow rays.  A walk that reaches the light adds its estimate to the path's
 // radiance; one that meets an interface leaves its next ray in the same slot and counts in pb.shContinue.
+template <int EXT>
 __global__ void __launch_bounds__(kShadeBlock, B2_VOL_MIN_BLOCKS)
 ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth, int kind) {
     int qi = blockIdx.x * blockDim.x + threadIdx.x;
@@ -453,7 +454,7 @@ ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth, int kind) {
     }
     uint32_t hit[6];
     for (int i = 0; i < 6; ++i) hit[i] = pb.shHits[6ll * t + i];
-    int res = ShadowTrSegment(rs, pb.scalars[path], sh, hit, T, rl, ru);
+    int res = ShadowTrSegment<EXT>(rs, pb.scalars[path], sh, hit, T, rl, ru);
     if (res == SHADOW_CONTINUE) {
         StoreRay(pb.shRays, t, sh.o, sh.d, ray[6]);
         a[2] = (uint32_t)sh.medium;
@@ -597,16 +598,24 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
                         int nActive, uint32_t matMask, cudaStream_t stream, int *launches) {
     int grid = Blocks(nActive, kShadeBlock);
     const bool lbvh = rs.integrator.lightSampler == 2, vol = rs.integrator.type == 1;
+    const bool ext = rs.geomExt != 0;  // patches / per-vertex normals or uv somewhere in the scene
+#define B2_SHADE_EXT(MAT, L, V)                                                                         \
+    do {                                                                                                \
+        if (ext)                                                                                        \
+            ShadeKernel<MAT, L, V, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
+        else                                                                                            \
+            ShadeKernel<MAT, L, V, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
+    } while (0)
 #define B2_SHADE(bit, MAT)                                                                              \
     if (matMask & (bit)) {                                                                              \
         if (vol && lbvh)                                                                                \
-            ShadeKernel<MAT, 1, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
+            B2_SHADE_EXT(MAT, 1, 1);                                                                    \
         else if (vol)                                                                                   \
-            ShadeKernel<MAT, 0, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
+            B2_SHADE_EXT(MAT, 0, 1);                                                                    \
         else if (lbvh)                                                                                  \
-            ShadeKernel<MAT, 1, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
+            B2_SHADE_EXT(MAT, 1, 0);                                                                    \
         else                                                                                            \
-            ShadeKernel<MAT, 0, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);    \
+            B2_SHADE_EXT(MAT, 0, 0);                                                                    \
         ++*launches;                                                                                    \
     }
     B2_SHADE(1u, MAT_DIFFUSE)
@@ -614,6 +623,7 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
     B2_SHADE(4u, MAT_DIELECTRIC)
     B2_SHADE(8u, MAT_COATED_DIFFUSE)
 #undef B2_SHADE
+#undef B2_SHADE_EXT
     return cudaGetLastError();
 }
 constexpr int kVolWarpGrid = 148 * 16;  // persistent-style grid of the warp-per-ray kernels (stride loop over the list)
@@ -630,10 +640,18 @@ cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int
             VolMediumWarpKernel<0><<<g, kVolWarpBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
     }
     for (int kind = 0; kind < 2 && !warpPerRay; ++kind) {
-        if (rs.integrator.lightSampler == 2)
-            VolMediumKernel<1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
-        else
-            VolMediumKernel<0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+        const bool lb = rs.integrator.lightSampler == 2;
+        if (rs.geomExt) {
+            if (lb)
+                VolMediumKernel<1, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+            else
+                VolMediumKernel<0, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+        } else {
+            if (lb)
+                VolMediumKernel<1, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+            else
+                VolMediumKernel<0, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+        }
     }
     return cudaGetLastError();
 }
@@ -648,8 +666,10 @@ cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int 
         if (warpPerRay && kind > 0)
             ShadowTrWarpKernel<<<(int)std::min<long long>(kVolWarpGrid, Blocks(nActive, kVolWarpBlock / 32)), kVolWarpBlock, 0,
                                  stream>>>(rs, pb, depth, kind);
+        else if (rs.geomExt)
+            ShadowTrKernel<1><<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
         else
-            ShadowTrKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
+            ShadowTrKernel<0><<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
     }
     return cudaGetLastError();
 }

@@ -112,7 +112,59 @@ B2_HD float TraceLensesFromFilm(const float *lens, int nLens, V3 co, V3 cd, V3 *
     return 1;
 }
 
-// RealisticCamera::GenerateRay (cameras.cpp:990-1019) with SampleExitPupil (:968-988).  Returns the
+// OmniCamera::TraceLensesFromFilm with TraceElement (cameras.cpp:2823-2989) for the main lens (no microlens array, no
+// aperture image, default ConvexQuadf bounds = no extra clipping): as the RealisticCamera's, but every ray
+// transform is a Transform::operator()(Ray) (Scale(1,1,-1) in and out, the interface's inverse transform per
+// element - each one nudges the origin along d by its error bound, identity included), the hit distance is found
+// on the element-space ray and applied to the lens-space ray, and the aperture is tested in both spaces.
+// The chromatic-aberration switch is not restated: it reads Ray::wavelength of a default-constructed Ray
+// (cameras.cpp:3352, ray.h:29), an indeterminate value on the CPU build; at the documented initial 550 nm it is a no-op.
+B2_HD float OmniTraceLensesFromFilm(const float *lens, int nLens, V3 co, V3 cd, V3 *oOut, V3 *dOut) {
+    const float flipZ[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, -1, 0, 0, 0, 0, 1};
+    float elementZ = 0;
+    V3 o, d;
+    TransformRay(flipZ, co, cd, o, d);
+    for (int i = nLens - 1; i >= 0; --i) {
+        const float *el = lens + 4 * i;
+        const float *xf = lens + 4 * nLens + 32 * i, *xfInv = xf + 16;
+        float curvatureRadius = el[0], eta = el[2], apertureRadius = el[3];
+        elementZ -= el[1];
+        bool isStop = curvatureRadius == 0;
+        // TraceElement
+        V3 eo, ed;
+        TransformRay(xfInv, o, d, eo, ed);
+        float t;
+        V3 n = mk(0, 0, 0);
+        if (isStop) {
+            t = (elementZ - eo.z) / ed.z;
+            if (ed.z == 0.0f || t < 0) return 0;
+        } else {
+            float zCenter = elementZ + curvatureRadius;
+            if (!IntersectSphericalElement(curvatureRadius, zCenter, eo, ed, &t, &n)) return 0;
+        }
+        // element.transform(n): a Normal3f goes through the inverse's transpose (util/transform.h:329-334)
+        n = mk(xfInv[0] * n.x + xfInv[4] * n.y + xfInv[8] * n.z, xfInv[1] * n.x + xfInv[5] * n.y + xfInv[9] * n.z,
+               xfInv[2] * n.x + xfInv[6] * n.y + xfInv[10] * n.z);
+        V3 eHit = eo + ed * t;
+        if (eHit.x * eHit.x + eHit.y * eHit.y > apertureRadius * apertureRadius) return 0;
+        // back in TraceLensesFromFilm
+        V3 pHit = o + d * t;
+        if (SqrF(pHit.x) + SqrF(pHit.y) > SqrF(apertureRadius)) return 0;
+        if (!isStop) {
+            o = pHit;
+            V3 w;
+            float eta_i = eta;
+            float eta_t = (i > 0 && lens[4 * (i - 1) + 2] != 0) ? lens[4 * (i - 1) + 2] : 1.f;
+            if (!Refract(Normalize(-d), n, eta_t / eta_i, nullptr, &w)) return 0;
+            d = w;
+        }
+    }
+    TransformRay(flipZ, o, d, *oOut, *dOut);
+    return 1;
+}
+
+// RealisticCamera::GenerateRay (cameras.cpp:990-1019) with SampleExitPupil (:968-988); OmniCamera::GenerateRay
+// (:3329-3373) is the same around its own lens trace.  Returns the
 // ray's weight; 0 = no ray (vignetted or no exit pupil at this film radius).
 B2_HD float GenerateRealisticRay(const CameraDev &c, const FilmDev &film, float pFilmX, float pFilmY, float uLens0,
                                  float uLens1, V3 &o, V3 &d) {
@@ -135,7 +187,8 @@ B2_HD float GenerateRealisticRay(const CameraDev &c, const FilmDev &film, float 
     V3 pPupil = mk(cosTheta * lx - sinTheta * ly, sinTheta * lx + cosTheta * ly, lensRearZ);
     V3 fd = pPupil - pFilm;
     V3 ro, rd;
-    float weight = TraceLensesFromFilm(c.lens, c.nLens, pFilm, fd, &ro, &rd);
+    float weight = c.type == 2 ? OmniTraceLensesFromFilm(c.lens, c.nLens, pFilm, fd, &ro, &rd)
+                               : TraceLensesFromFilm(c.lens, c.nLens, pFilm, fd, &ro, &rd);
     if (weight == 0) return 0;
     TransformRay(c.renderFromCamera, ro, rd, o, d);
     d = Normalize(d);

@@ -25,8 +25,8 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         return B200PT_ERR_INVALID;
     };
     if (!d) return bad("null render description");
-    if (d->camera_type > 1) return bad("unsupported camera type (0 perspective, 1 realistic)");
-    if (d->camera_type == 1) {
+    if (d->camera_type > 2) return bad("unsupported camera type (0 perspective, 1 realistic, 2 omni)");
+    if (d->camera_type >= 1) {
         if (d->n_lens_elements < 1 || d->n_lens_elements > 64 || !d->lens_elements)
             return bad("realistic camera: 1..64 lens elements needed");
         if (d->n_exit_pupil_bounds < 1 || !d->exit_pupil_bounds) return bad("realistic camera: exit pupil bounds missing");
@@ -60,8 +60,16 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     rs.camera.type = d->camera_type;
     rs.camera.lens = rs.camera.pupilBounds = nullptr;
     rs.camera.nLens = rs.camera.nPupilBounds = 0;
-    if (d->camera_type == 1) {
+    if (d->camera_type >= 1) {
         out.lens.assign(d->lens_elements, d->lens_elements + 4 * size_t(d->n_lens_elements));
+        if (d->camera_type == 2) {  // the interfaces' transforms follow the table: lens[4 n + 32 i]
+            static const float ident[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+            for (uint32_t i = 0; i < d->n_lens_elements; ++i)
+                for (int h = 0; h < 2; ++h) {
+                    const float *m = d->lens_element_transforms ? d->lens_element_transforms + 32 * size_t(i) + 16 * h : ident;
+                    out.lens.insert(out.lens.end(), m, m + 16);
+                }
+        }
         out.pupilBounds.assign(d->exit_pupil_bounds, d->exit_pupil_bounds + 4 * size_t(d->n_exit_pupil_bounds));
         rs.camera.nLens = int32_t(d->n_lens_elements);
         rs.camera.nPupilBounds = int32_t(d->n_exit_pupil_bounds);
@@ -210,6 +218,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         }
         out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, nOff, mi, mo, uvOff, 0};
     }
+    out.rs.geomExt = (hs.hasPatches || !out.cornerAttr.empty()) ? 1u : 0u;
     out.lights.resize(d->n_lights);
     for (uint32_t i = 0; i < d->n_lights; ++i) {
         const b200pt_light &l = d->lights[i];

@@ -79,7 +79,7 @@ B2_HD void GenerateCameraPath(const RenderSceneDev &rs, PathRegs &p, int px, int
     ZSobolGet2D(s, l0, l1);
     p.dimension = s.dimension;
     p.cameraWeight = 1.f;
-    if (rs.camera.type == 1)
+    if (rs.camera.type >= 1)  // realistic, omni
         p.cameraWeight = GenerateRealisticRay(rs.camera, rs.film, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
     else
         GeneratePerspectiveRay(rs.camera, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
@@ -265,7 +265,7 @@ B2_SPECTRAL_LOOP
 // VOL: 1 = the surface half of VolPathIntegrator::Li (cpu/integrators.cpp:1100-1268): MIS through the rescaled path
 // probabilities r_u / r_l (IO::Ru / Rl), interface surfaces are crossed, light samples carry what the
 // transmittance walk needs (IO::ShadowEndVol), the ray's medium follows the surface's MediumInterface.
-template <class IO, int MAT = -1, int LBVH = -1, int VOL = -1>
+template <class IO, int MAT = -1, int LBVH = -1, int VOL = -1, int EXT = 1>
 B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit[6], IO &io) {
     const bool lightBvh = LBVH < 0 ? rs.integrator.lightSampler == 2 : LBVH == 1;
     const bool vol = VOL < 0 ? rs.integrator.type == 1 : VOL == 1;
@@ -296,10 +296,10 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
         V3 dInst = mk(mi[0] * p.rayD.x + mi[1] * p.rayD.y + mi[2] * p.rayD.z,
                       mi[4] * p.rayD.x + mi[5] * p.rayD.y + mi[6] * p.rayD.z,
                       mi[8] * p.rayD.x + mi[9] * p.rayD.y + mi[10] * p.rayD.z);
-        si = SlotInteraction(rs.prims, slot, tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, slot, tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
         TransformSurfHit(in, si);
     } else {
-        si = SlotInteraction(rs.prims, slot, tv, b0, b1, b2, wo, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, slot, tv, b0, b1, b2, wo, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
     }
 
     // ---- emitted light at the hit (cpu/integrators.cpp:664-679)
@@ -321,7 +321,7 @@ B2_SPECTRAL_LOOP
                     float pmf = al.aliasP;
                     if (rs.integrator.lightSampler == 0) pmf = 1.f / rs.nLights;
                     if (lightBvh) pmf = LightBvhPMF(rs, Mid(p.prev.pi), p.prev.ns, mesh.lightFirst + (int)tv.tri);
-                    float p_l = pmf * ShapePDF(rs.prims, slot, tv, p.prev, p.rayD, al.flipNormal != 0);
+                    float p_l = pmf * ShapePDF<EXT>(rs.prims, slot, tv, p.prev, p.rayD, al.flipNormal != 0);
                     for (int k = 0; k < kNLambda; ++k) io.SetRl(k, io.Rl(k) * p_l);
                     avg = AvgRuRl(io);
                 }
@@ -339,7 +339,7 @@ B2_SPECTRAL_LOOP
                 if (rs.integrator.lightSampler == 0) pmf = 1.f / rs.nLights;
                 if (lightBvh)
                     pmf = LightBvhPMF(rs, Mid(p.prev.pi), p.prev.ns, mesh.lightFirst + (int)tv.tri);
-                float p_l = pmf * ShapePDF(rs.prims, slot, tv, p.prev, p.rayD, al.flipNormal != 0);
+                float p_l = pmf * ShapePDF<EXT>(rs.prims, slot, tv, p.prev, p.rayD, al.flipNormal != 0);
                 w = PowerHeuristic(p.pB, p_l);
             }
             const SpectrumTable &sp = rs.spectra[al.spectrum];
@@ -427,7 +427,7 @@ B2_SPECTRAL_LOOP
             ss.ok = false;
             if (lidx >= 0 && light.type == 0) {
                 TriVerts lt = LoadTri(rs.prims, light.slot);
-                ss = SampleShapeSolidAngle(rs.prims, light.slot, lt, ctx, uLight0, uLight1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri).n);
+                ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, uLight0, uLight1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri).n);
             }
             V3 cp = Mid(ctx.pi);
             if (ss.ok && ss.pdf != 0 && LengthSquared(Mid(ss.pi) - cp) != 0) {

@@ -133,8 +133,11 @@ B2_HD_CALL SurfHit PatchInteraction(const PatchVerts &t, float u, float v, V3 wo
 }
 
 // Shape::Intersect's interaction for either kind of slot; (b1, b2) of a patch record are its (u, v)
+// EXT = 0: the scene has triangles without per-vertex attributes only (RenderSceneDev::geomExt), the plain path
+template <int EXT = 1>
 B2_HD SurfHit SlotInteraction(const void *prims, uint32_t slot, const TriVerts &t, float b0, float b1, float b2, V3 wo,
                               bool flipNormal, CornerAttr ca) {
+    if (EXT == 0) return TriangleInteraction(t, b0, b1, b2, wo, flipNormal);
     if (t.kind == 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
         return PatchInteraction(pv, b1, b2, wo, flipNormal);
@@ -658,15 +661,19 @@ B2_HD float TrianglePDF(const TriVerts &t, const LightCtx &ctx, V3 wi, bool flip
 
 
 // Shape::Sample(ctx, u) / Shape::PDF(ctx, wi) of the emitter in slot `t`
+template <int EXT = 1>
 B2_HD ShapeSampleOut SampleShapeSolidAngle(const void *prims, uint32_t slot, const TriVerts &t, const LightCtx &ctx, float u0,
                                            float u1, bool flipNormal, const float *cn) {
+    if (EXT == 0) return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal);
     if (t.kind == 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
         return SamplePatchSolidAngle(pv, ctx, u0, u1, flipNormal);
     }
     return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal, cn);
 }
+template <int EXT = 1>
 B2_HD float ShapePDF(const void *prims, uint32_t slot, const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
+    if (EXT == 0) return TrianglePDF(t, ctx, wi, flipNormal);
     if (t.kind == 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
         return PatchPDF(pv, ctx, wi, flipNormal);

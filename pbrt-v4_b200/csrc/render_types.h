@@ -70,12 +70,13 @@ struct MediumDev {
 };
 
 struct CameraDev {
-    uint32_t type;               // 0 perspective (cameras.cpp:433-456), 1 realistic (cameras.cpp:820-1019)
+    uint32_t type;               // 0 perspective (cameras.cpp:433-456), 1 realistic (cameras.cpp:820-1019), 2 omni (:2823-3373)
     float cameraFromRaster[16];  // row major
     float renderFromCamera[16];
     float lensRadius, focalDistance;
     // realistic: lens elements {curvatureRadius, thickness, eta, apertureRadius} front to rear (metres),
     // exit-pupil bounds {xmin, ymin, xmax, ymax} per film-radius bin, film extent and diagonal
+    // omni: the interfaces' {transform[16], inverse[16]} follow the table at lens[4 nLens + 32 i]
     const float *lens;
     const float *pupilBounds;
     int32_t nLens, nPupilBounds;
@@ -133,6 +134,7 @@ struct RenderSceneDev {
     float lightBvhBounds[6];
     const MediumDev *media;
     uint32_t nMedia;
+    uint32_t geomExt;         // some mesh is a bilinear patch mesh or has per-corner attributes (else the EXT = 0 kernels run)
     const float *cornerAttr;  // per-corner normals / uv of the meshes that have them (MeshAttrDev::nOff, uvOff)
 };
 

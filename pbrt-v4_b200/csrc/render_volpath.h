@@ -8,6 +8,7 @@
 namespace b200pt {
 
 // SurfaceInteraction of a closest-hit record for a ray with direction rayD (as ShadeVertex builds it)
+template <int EXT = 1>
 B2_HD SurfHit SurfHitFromRecord(const RenderSceneDev &rs, V3 rayD, const uint32_t hit[6], uint32_t *meshOut) {
     float b0, b1, b2;
     memcpy(&b0, &hit[2], 4);
@@ -22,10 +23,10 @@ B2_HD SurfHit SurfHitFromRecord(const RenderSceneDev &rs, V3 rayD, const uint32_
         const float *mi = in.mInv;
         V3 dInst = mk(mi[0] * rayD.x + mi[1] * rayD.y + mi[2] * rayD.z, mi[4] * rayD.x + mi[5] * rayD.y + mi[6] * rayD.z,
                       mi[8] * rayD.x + mi[9] * rayD.y + mi[10] * rayD.z);
-        si = SlotInteraction(rs.prims, hit[0], tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, hit[0], tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
         TransformSurfHit(in, si);
     } else {
-        si = SlotInteraction(rs.prims, hit[0], tv, b0, b1, b2, -rayD, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, hit[0], tv, b0, b1, b2, -rayD, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
     }
     return si;
 }
@@ -44,7 +45,7 @@ struct LightPick {
     ShapeSampleOut ss;
     V3 wi;
 };
-template <int LBVH>
+template <int LBVH, int EXT = 1>
 B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx, float uL, float u0, float u1) {
     const bool lightBvh = LBVH < 0 ? rs.integrator.lightSampler == 2 : LBVH == 1;
     LightPick lp;
@@ -67,7 +68,7 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
     const LightDev &light = rs.lights[lp.lidx];
     if (light.type != 0) return lp;  // infinite lights give nothing under allowIncompletePDF
     TriVerts lt = LoadTri(rs.prims, light.slot);
-    lp.ss = SampleShapeSolidAngle(rs.prims, light.slot, lt, ctx, u0, u1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri).n);
+    lp.ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, u0, u1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri).n);
     V3 cp = Mid(ctx.pi);
     if (!lp.ss.ok || lp.ss.pdf == 0 || LengthSquared(Mid(lp.ss.pi) - cp) == 0) return lp;
     lp.wi = Normalize(Mid(lp.ss.pi) - cp);
@@ -94,7 +95,7 @@ enum { VOL_SURVIVE = 0, VOL_TERMINATED = 1, VOL_SCATTERED = 2 };
 
 // The `if (ray.medium)` block of VolPathIntegrator::Li for the ray p.ray with closest hit at tHit (INFINITY = none).
 // IO adds Ru/SetRu/Rl/SetRl (rescaled path probabilities) and ShadowEndVol to ShadeVertex's IO.
-template <class IO, int LBVH = -1>
+template <class IO, int LBVH = -1, int EXT = 1>
 B2_HD int VolMediumStep(const RenderSceneDev &rs, PathRegs &p, float tHit, IO &io) {
     const MediumDev &m = rs.media[p.medium];
     ZSobol s = SamplerFor(rs, p);
@@ -128,7 +129,7 @@ B2_SPECTRAL_LOOP
     float uL = ZSobolGet1D(s);
     float uLight0, uLight1;
     ZSobolGet2D(s, uLight0, uLight1);
-    LightPick lp = PickAndSampleLight<LBVH>(rs, ctx, uL, uLight0, uLight1);
+    LightPick lp = PickAndSampleLight<LBVH, EXT>(rs, ctx, uL, uLight0, uLight1);
     if (lp.ok) {
         float fHat = HenyeyGreenstein(Dot(woN, lp.wi), m.g);
         if (fHat != 0) {
@@ -184,13 +185,14 @@ struct ShadowRegs {
 enum { SHADOW_BLOCKED = 0, SHADOW_REACHED = 1, SHADOW_CONTINUE = 2 };
 // T_ray / r_l / r_u: the walk's running products (all ones before the first segment).  hit: closest hit of
 // (o, d, 1 - ShadowEpsilon).  SHADOW_CONTINUE leaves the next segment's ray in sh.
+template <int EXT = 1>
 B2_HD int ShadowTrSegment(const RenderSceneDev &rs, float lambdaU, ShadowRegs &sh, const uint32_t hit[6], float *T_ray,
                           float *r_l, float *r_u) {
     const bool isHit = hit[0] != kMissTag;
     uint32_t meshId = 0;
     SurfHit si;
     if (isHit) {
-        si = SurfHitFromRecord(rs, sh.d, hit, &meshId);
+        si = SurfHitFromRecord<EXT>(rs, sh.d, hit, &meshId);
         if (rs.meshes[meshId].material >= 0) return SHADOW_BLOCKED;  // an opaque surface
     }
     if (sh.medium >= 0) {

@@ -65,7 +65,7 @@ class RenderScene:
         r = capi.RenderDesc()
         r.camera_type = int(d["camera_type"][0])
         r.render_from_camera[:] = [float(x) for x in d["render_from_camera"]]
-        if r.camera_type == 1:  # RealisticCamera: lens table + exit-pupil bounds from the host
+        if r.camera_type in (1, 2):  # RealisticCamera / OmniCamera: lens table + exit-pupil bounds from the host
             lens = np.ascontiguousarray(d["camera_lens"], np.float32).reshape(-1, 4)
             pupil = np.ascontiguousarray(d["camera_exit_pupil"], np.float32).reshape(-1, 4)
             r.n_lens_elements, r.lens_elements = len(lens), capi.fptr(lens)
@@ -73,6 +73,11 @@ class RenderScene:
             r.physical_extent[:] = [float(x) for x in d["camera_extent"][:4]]
             r.film_diagonal = float(d["camera_extent"][4])
             keep += [lens, pupil]
+            if r.camera_type == 2 and "camera_lens_transforms" in d:
+                xf = np.ascontiguousarray(d["camera_lens_transforms"], np.float32).reshape(-1, 32)
+                assert len(xf) == len(lens)
+                r.lens_element_transforms = capi.fptr(xf)
+                keep.append(xf)
         else:
             r.camera_from_raster[:] = [float(x) for x in d["camera_from_raster"]]
             r.lens_radius, r.focal_distance = float(d["camera_params"][0]), float(d["camera_params"][1])

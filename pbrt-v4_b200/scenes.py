@@ -582,7 +582,7 @@ def chart_spectra(n=24, seed=2404):
 
 
 def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0, nbuckets=31, aperture_mm=12.0,
-                 focus=1.9, film="spectral", crop=None):
+                 focus=1.9, film="spectral", crop=None, camera="realistic", chromatic=False):
     """BASELINE configs[3]: the Cornell room with a 24-patch spectral reflectance chart on the back wall, seen
     through a RealisticCamera (double-Gauss 50 mm lens file written next to the scene) onto a SpectralFilm
     with `nbuckets` bands over 395..705 nm (the ISET 31-band setting)."""
@@ -592,13 +592,34 @@ def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0,
         f.write("# double-Gauss 50 mm: radius thickness eta aperture-diameter (mm)\n")
         for e in DGAUSS_50MM:
             f.write(" ".join(repr(float(x)) for x in e) + "\n")
+    if camera == "omni":
+        # the ISET OmniCamera reads the same prescription as JSON (cameras.cpp:3812-3960): per surface radius,
+        # thickness, ior, semi_aperture (mm) and an optional 3x3 + translation transform; two elements are
+        # decentred / tilted here so the per-element transforms matter
+        import json
+        surfaces = []
+        for k, (radius, thick, eta, diam) in enumerate(DGAUSS_50MM):
+            surf = {"radius": radius, "thickness": thick, "ior": eta if eta else 1.0, "semi_aperture": diam / 2,
+                    "conic_constant": 0.0}
+            if k == 2:
+                surf["transform"] = [[1, 0, 0], [0, 1, 0], [0, 0, 1], [0.15, -0.1, 0.0]]
+            if k == 7:
+                c, sn = float(np.cos(0.01)), float(np.sin(0.01))
+                surf["transform"] = [[c, 0, -sn], [0, 1, 0], [sn, 0, c], [0.0, 0.05, 0.0]]
+            surfaces.append(surf)
+        lens = os.path.splitext(path)[0] + "_lens.json"
+        with open(lens, "w") as f:
+            json.dump({"name": "dgauss50", "description": "double-Gauss 50 mm", "surfaces": surfaces}, f)
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     colours = [white, white, white, red, green, None, white, white]
     cropw = f' "float cropwindow" [{crop[0]} {crop[1]} {crop[2]} {crop[3]}]' if crop else ''
     lines = [
         'LookAt 0.5 0.5 -1.4  0.5 0.5 0.5  0 1 0',
-        f'Camera "realistic" "string lensfile" "{lens}" "float aperturediameter" {aperture_mm} '
-        f'"float focusdistance" {focus}',
+        f'Camera "{camera}" "string lensfile" "{lens}" "float aperturediameter" {aperture_mm} '
+        f'"float focusdistance" {focus}' + (' "bool chromaticAberrationEnabled" true' if chromatic else '')
+        # with decentred elements the reference's thick-lens focusing diverges: the film distance is given instead
+        # (the value FocusThickLens finds for the centred prescription at this focus distance)
+        + (' "float filmdistance" 0.0375136' if camera == "omni" else ''),
         f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
         f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "power"',
         'PixelFilter "box"',

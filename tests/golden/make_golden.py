@@ -113,6 +113,19 @@ def make_config4_goldens(P, refrun, out):
         print("config4_small", img.shape, names[:4], "mean", img[..., :3].mean(axis=(0, 1)), f"{secs:.2f}s")
 
 
+def make_omni_goldens(P, refrun, out):
+    """the config-4 scene through the ISET OmniCamera (JSON prescription, two decentred / tilted
+    interfaces), spectral film."""
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        pbrt = os.path.join(tmp, "omni.pbrt")
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "omni.exr"), camera="omni", **CONFIG4_SMALL)
+        refrun.dump_scene(pbrt, os.path.join(out, "omni_small.b2rs"))
+        img, names, secs = refrun.render_channels(pbrt)
+        np.save(os.path.join(out, "omni_small_ref.npy"), img.astype(np.float32))
+        print("omni_small", img.shape, "mean", img[..., :3].mean(axis=(0, 1)), f"{secs:.2f}s")
+
+
 # BASELINE.json configs[4] (scenes.config5_pbrt): VolPathIntegrator, homogeneous fog + a grid medium inside an
 # interface shell.  In miniature (24^3 density) with the reference's image at two seeds; the full-size tables
 # (256^3 density, 1920x1080, 512 spp) are derived from the small ones by bench.py (the grid alone is 67 MB).
@@ -187,6 +200,9 @@ if __name__ == "__main__":
     elif "--config5-only" in sys.argv:
         make_config5_goldens(P, refrun, out)
         sys.exit(0)
+    if "--omni-only" in sys.argv:
+        make_omni_goldens(P, refrun, out)
+        sys.exit(0)
     if "--config4-only" in sys.argv:
         make_config4_goldens(P, refrun, out)
         sys.exit(0)
@@ -194,6 +210,7 @@ if __name__ == "__main__":
         make_render_goldens(P, refrun, out)
         if not os.environ.get("B200PT_GOLDEN_CASES"):
             make_config4_goldens(P, refrun, out)
+            make_omni_goldens(P, refrun, out)
             make_config5_goldens(P, refrun, out)
     if "--render-only" in sys.argv:
         sys.exit(0)

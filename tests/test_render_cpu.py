@@ -153,6 +153,26 @@ def test_golden_image_config4_realistic_camera(P, rendercheck):
     np.testing.assert_array_equal(rgbw[..., 3], float(rsc.spp))
 
 
+def test_golden_image_omni_camera(P, rendercheck):
+    """the ISET OmniCamera (cameras.cpp:2823-2989, 3329-3373) without a microlens array: the config-4
+    scene through a JSON prescription with a decentred and a tilted interface (per-element transforms), 31-band
+    spectral film.  Path-for-path agreement with the reference's image, and the transforms have to matter."""
+    name = "omni_small"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    assert int(rsc.d["camera_type"][0]) == 2 and rsc.n_buckets == 31
+    rgbw, bsum, wsum = rendercheck(rsc, full=True)
+    img = P.render.film_to_image(rgbw, rsc.d["film_matrix"])
+    assert rrmse(img, ref[..., :3]) <= TOL_RRMSE
+    assert abs(img.mean() - ref[..., :3].mean()) <= TOL_MEAN * ref[..., :3].mean()
+    spec = np.where(wsum > 0, bsum / np.where(wsum > 0, wsum, 1), 0).astype(np.float32).transpose(1, 2, 0)
+    assert rrmse(spec, ref[..., 3:]) <= TOL_RRMSE
+    d = dict(rsc.d)
+    d.pop("camera_lens_transforms")  # all interfaces centred: a different image
+    img0 = P.render.film_to_image(rendercheck(P.RenderScene(d)), rsc.d["film_matrix"])
+    assert rrmse(img0, ref[..., :3]) > 100 * TOL_RRMSE
+
+
 def test_realistic_camera_description_is_validated(P, rendercheck):
     rsc = P.RenderScene.load(os.path.join(GOLD, "config4_small.b2rs"))
     d = dict(rsc.d)

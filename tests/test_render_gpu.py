@@ -179,10 +179,11 @@ def test_spectral_image_needs_a_spectral_film(P, cornell):
         r.close()
 
 
-def test_config4_realistic_camera_spectral(P, rendercheck):
+@pytest.mark.parametrize("name", ["config4_small", "omni_small"])
+def test_config4_realistic_camera_spectral(P, rendercheck, name):
     """BASELINE configs[3] in miniature on the device: RealisticCamera rays + 31-band SpectralFilm against the
-    reference's Film::GetImage, and against the CPU loop over the same headers."""
-    name = "config4_small"
+    reference's Film::GetImage, and against the CPU loop over the same headers.  omni_small: the same scene through
+    the ISET OmniCamera with decentred / tilted interfaces."""
     rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
     ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
     r = P.B200Renderer(rsc)
