@@ -311,6 +311,19 @@ typedef struct b200pt_render_desc {
      * LensElementInterface::transform of each interface (cameras.h:856-878; decentred / tilted elements), NULL =
      * all identity. */
     const float *lens_element_transforms;
+    /* camera_type 2 with a microlens array in front of the sensor (OmniCamera::microlens, cameras.h:940-960;
+     * TraceFullLensSystemFromFilm cameras.cpp:3259-3327, SampleMicrolensPupil :3167-3187,
+     * MicrolensElementFromIndex :3221-3244): n_microlens_elements > 0 switches it on.  microlens_elements /
+     * microlens_element_transforms as for the main lens; microlens_dims = lenses across the film in x and y;
+     * microlens_offsets = dims[0] * dims[1] x {dx, dy} (metres, row y * dims[0] + x); microlens_offset_from_sensor
+     * and microlens_simulation_radius as the OmniCamera object holds them (microlens.simulationRadius). */
+    uint32_t n_microlens_elements;
+    const float *microlens_elements;
+    const float *microlens_element_transforms;
+    int32_t microlens_dims[2];
+    const float *microlens_offsets;
+    float microlens_offset_from_sensor;
+    int32_t microlens_simulation_radius;
 } b200pt_render_desc;
 
 typedef struct b200pt_render b200pt_render;

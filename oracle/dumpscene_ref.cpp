@@ -299,7 +299,33 @@ int main(int argc, char **argv) {
         // rigid transform per element interface and the chromatic-aberration switch
         const OmniCamera *oc = camera.Cast<OmniCamera>();
         if (oc->apertureImage) die("aperture images are not dumped");
-        if (oc->microlens.elementInterfaces.size() > 0) die("microlens arrays are not dumped");
+        if (oc->microlens.elementInterfaces.size() > 0) {
+            // the microlens array (cameras.h:940-960): interfaces + transforms as for the main lens, the grid, the
+            // per-lens centre offsets, and the two scalars TraceFullLensSystemFromFilm / SampleMicrolensPupil read
+            // (microlens.simulationRadius is assigned from a not yet initialised member in the constructor,
+            // cameras.cpp:2530 - the value the object really holds is what is dumped)
+            std::vector<float> ml, mxf, off;
+            for (const auto &e : oc->microlensElementInterfaces) {
+                if (e.asphericCoefficients.size() > 0) die("aspheric elements are not dumped");
+                ml.insert(ml.end(), {e.curvatureRadius.x, e.thickness, e.eta, e.apertureRadius.x});
+                std::vector<float> m = Mat(e.transform.GetMatrix()), mi = Mat(e.transform.GetInverseMatrix());
+                mxf.insert(mxf.end(), m.begin(), m.end());
+                mxf.insert(mxf.end(), mi.begin(), mi.end());
+            }
+            Vector2i dims = oc->microlensDimensions;
+            if (oc->microlens.dimensions != dims) die("microlens dimensions disagree");
+            if (oc->microlensOffsets.size() != size_t(dims.x) * dims.y) die("microlens offsets missing");
+            for (const Vector2f &o : oc->microlensOffsets) off.insert(off.end(), {o.x, o.y});
+            int R = oc->microlens.simulationRadius;
+            if (R < 0 || R > 8) die("microlens.simulationRadius holds an indeterminate value in this run");
+            w.f32("microlens_lens", {uint32_t(ml.size() / 4), 4}, ml);
+            w.f32("microlens_transforms", {uint32_t(mxf.size() / 32), 32}, mxf);
+            w.f32("microlens_offsets", {uint32_t(off.size() / 2), 2}, off);
+            w.i32("microlens_ints", {3}, {dims.x, dims.y, R});
+            w.f32("microlens_params", {1}, {oc->microlens.offsetFromSensor});
+            fprintf(stderr, "dumpscene_ref: microlens %d x %d, simulation radius %d (asked: %d)\n", dims.x, dims.y, R,
+                    oc->microlensSimulationRadius);
+        }
         w.u32("camera_type", {1}, {2});
         w.f32("render_from_camera", {16}, Mat(oc->cameraTransform.renderFromCamera.startTransform.GetMatrix()));
         std::vector<float> lens, pupil, xf;

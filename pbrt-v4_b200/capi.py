@@ -165,7 +165,11 @@ class RenderDesc(C.Structure):
                 ("physical_extent", C.c_float * 4), ("film_diagonal", C.c_float),
                 ("integrator_type", C.c_uint32), ("n_media", C.c_uint32), ("media", C.POINTER(Medium)),
                 ("mesh_media", C.POINTER(C.c_int32)), ("camera_medium", C.c_int32),
-                ("lens_element_transforms", C.POINTER(C.c_float))]
+                ("lens_element_transforms", C.POINTER(C.c_float)),
+                ("n_microlens_elements", C.c_uint32), ("microlens_elements", C.POINTER(C.c_float)),
+                ("microlens_element_transforms", C.POINTER(C.c_float)), ("microlens_dims", C.c_int32 * 2),
+                ("microlens_offsets", C.POINTER(C.c_float)), ("microlens_offset_from_sensor", C.c_float),
+                ("microlens_simulation_radius", C.c_int32)]
 
 
 class RenderStats(C.Structure):

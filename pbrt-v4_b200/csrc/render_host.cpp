@@ -34,6 +34,14 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         for (uint32_t i = 0; i < d->n_lens_elements; ++i)
             if (d->lens_elements[4 * i] != 0 && d->lens_elements[4 * i + 2] == 0)
                 return bad("realistic camera: a curved element with eta 0");
+        if (d->camera_type == 2 && d->n_microlens_elements) {
+            // the reference reads elementInterfaces[i - 1].eta of the MAIN lens while tracing microlens interface i
+            if (d->n_microlens_elements > d->n_lens_elements) return bad("omni camera: more microlens interfaces than lens interfaces");
+            if (!d->microlens_elements || !d->microlens_offsets || d->microlens_dims[0] < 1 || d->microlens_dims[1] < 1)
+                return bad("omni camera: microlens tables missing");
+            if (d->microlens_simulation_radius < 0 || d->microlens_simulation_radius > 8)
+                return bad("omni camera: microlens simulation radius must be 0..8");
+        }
     }
     if (d->film_type > 1) return bad("unsupported film type");
     if (d->film_type == 1) {
@@ -60,6 +68,8 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     rs.camera.type = d->camera_type;
     rs.camera.lens = rs.camera.pupilBounds = nullptr;
     rs.camera.nLens = rs.camera.nPupilBounds = 0;
+    rs.camera.nMicro = rs.camera.microDimX = rs.camera.microDimY = rs.camera.microRadius = 0;
+    rs.camera.microOffsetFromSensor = 0;
     if (d->camera_type >= 1) {
         out.lens.assign(d->lens_elements, d->lens_elements + 4 * size_t(d->n_lens_elements));
         if (d->camera_type == 2) {  // the interfaces' transforms follow the table: lens[4 n + 32 i]
@@ -69,6 +79,23 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                     const float *m = d->lens_element_transforms ? d->lens_element_transforms + 32 * size_t(i) + 16 * h : ident;
                     out.lens.insert(out.lens.end(), m, m + 16);
                 }
+            if (d->n_microlens_elements) {
+                const uint32_t nm = d->n_microlens_elements;
+                const size_t nl = size_t(d->microlens_dims[0]) * size_t(d->microlens_dims[1]);
+                out.lens.insert(out.lens.end(), d->microlens_elements, d->microlens_elements + 4 * size_t(nm));
+                for (uint32_t i = 0; i < nm; ++i)
+                    for (int h = 0; h < 2; ++h) {
+                        const float *m = d->microlens_element_transforms ? d->microlens_element_transforms + 32 * size_t(i) + 16 * h
+                                                                         : ident;
+                        out.lens.insert(out.lens.end(), m, m + 16);
+                    }
+                out.lens.insert(out.lens.end(), d->microlens_offsets, d->microlens_offsets + 2 * nl);
+                rs.camera.nMicro = int32_t(nm);
+                rs.camera.microDimX = d->microlens_dims[0];
+                rs.camera.microDimY = d->microlens_dims[1];
+                rs.camera.microRadius = d->microlens_simulation_radius;
+                rs.camera.microOffsetFromSensor = d->microlens_offset_from_sensor;
+            }
         }
         out.pupilBounds.assign(d->exit_pupil_bounds, d->exit_pupil_bounds + 4 * size_t(d->n_exit_pupil_bounds));
         rs.camera.nLens = int32_t(d->n_lens_elements);

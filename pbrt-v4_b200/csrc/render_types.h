@@ -83,6 +83,10 @@ struct CameraDev {
     float physicalExtent[4];     // Bounds2f {pMin.x, pMin.y, pMax.x, pMax.y}
     float filmDiagonal;
     int32_t medium;              // medium camera rays start in, -1 = none
+    // omni with a microlens array: its table, transforms and per-lens offsets follow the main lens's in `lens`:
+    // micro = lens + 36 nLens: [4 nMicro][32 nMicro][2 microDimX microDimY]
+    int32_t nMicro, microDimX, microDimY, microRadius;
+    float microOffsetFromSensor;
 };
 
 struct FilmDev {

@@ -78,6 +78,18 @@ class RenderScene:
                 assert len(xf) == len(lens)
                 r.lens_element_transforms = capi.fptr(xf)
                 keep.append(xf)
+            if r.camera_type == 2 and "microlens_lens" in d:
+                ml = np.ascontiguousarray(d["microlens_lens"], np.float32).reshape(-1, 4)
+                mxf = np.ascontiguousarray(d["microlens_transforms"], np.float32).reshape(-1, 32)
+                off = np.ascontiguousarray(d["microlens_offsets"], np.float32).reshape(-1, 2)
+                mi = [int(x) for x in d["microlens_ints"]]
+                assert len(mxf) == len(ml) and len(off) == mi[0] * mi[1]
+                r.n_microlens_elements, r.microlens_elements = len(ml), capi.fptr(ml)
+                r.microlens_element_transforms, r.microlens_offsets = capi.fptr(mxf), capi.fptr(off)
+                r.microlens_dims[:] = mi[:2]
+                r.microlens_simulation_radius = mi[2]
+                r.microlens_offset_from_sensor = float(d["microlens_params"][0])
+                keep += [ml, mxf, off]
         else:
             r.camera_from_raster[:] = [float(x) for x in d["camera_from_raster"]]
             r.lens_radius, r.focal_distance = float(d["camera_params"][0]), float(d["camera_params"][1])

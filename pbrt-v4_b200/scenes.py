@@ -582,7 +582,7 @@ def chart_spectra(n=24, seed=2404):
 
 
 def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0, nbuckets=31, aperture_mm=12.0,
-                 focus=1.9, film="spectral", crop=None, camera="realistic", chromatic=False):
+                 focus=1.9, film="spectral", crop=None, camera="realistic", chromatic=False, microlens=None):
     """BASELINE configs[3]: the Cornell room with a 24-patch spectral reflectance chart on the back wall, seen
     through a RealisticCamera (double-Gauss 50 mm lens file written next to the scene) onto a SpectralFilm
     with `nbuckets` bands over 395..705 nm (the ISET 31-band setting)."""
@@ -608,8 +608,21 @@ def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0,
                 surf["transform"] = [[c, 0, -sn], [0, 1, 0], [sn, 0, c], [0.0, 0.05, 0.0]]
             surfaces.append(surf)
         lens = os.path.splitext(path)[0] + "_lens.json"
+        spec = {"name": "dgauss50", "description": "double-Gauss 50 mm", "surfaces": surfaces}
+        if microlens:
+            # a microlens array in front of the sensor (light-field camera, cameras.cpp:3259-3327): `microlens` lenses
+            # across the film, each a thin biconvex element; per-lens centre offsets in metres (cameras.cpp:3950-3962)
+            n = int(microlens)
+            rng = np.random.default_rng(5)
+            spec["microlens"] = {
+                "dimensions": [n, n],
+                "offsets": [[float(a), float(b)] for a, b in rng.uniform(-2e-5, 2e-5, (n * n, 2))],
+                "surfaces": [
+                    {"radius": 1.2, "thickness": 0.3, "ior": 1.5, "semi_aperture": 0.9, "conic_constant": 0.0},
+                    {"radius": -1.5, "thickness": 0.6, "ior": 1.0, "semi_aperture": 0.9, "conic_constant": 0.0},
+                ]}
         with open(lens, "w") as f:
-            json.dump({"name": "dgauss50", "description": "double-Gauss 50 mm", "surfaces": surfaces}, f)
+            json.dump(spec, f)
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     colours = [white, white, white, red, green, None, white, white]
     cropw = f' "float cropwindow" [{crop[0]} {crop[1]} {crop[2]} {crop[3]}]' if crop else ''
@@ -619,7 +632,8 @@ def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0,
         f'"float focusdistance" {focus}' + (' "bool chromaticAberrationEnabled" true' if chromatic else '')
         # with decentred elements the reference's thick-lens focusing diverges: the film distance is given instead
         # (the value FocusThickLens finds for the centred prescription at this focus distance)
-        + (' "float filmdistance" 0.0375136' if camera == "omni" else ''),
+        + (' "float filmdistance" 0.0375136' if camera == "omni" else '')
+        + (' "float microlenssensoroffset" 0.0006 "integer microlenssimulationradius" 1' if microlens else ''),
         f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
         f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "power"',
         'PixelFilter "box"',

@@ -124,6 +124,12 @@ def make_omni_goldens(P, refrun, out):
         img, names, secs = refrun.render_channels(pbrt)
         np.save(os.path.join(out, "omni_small_ref.npy"), img.astype(np.float32))
         print("omni_small", img.shape, "mean", img[..., :3].mean(axis=(0, 1)), f"{secs:.2f}s")
+        # the same camera with a 24 x 24 microlens array in front of the sensor (light-field capture)
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "omni.exr"), camera="omni", microlens=24, **CONFIG4_SMALL)
+        refrun.dump_scene(pbrt, os.path.join(out, "omni_microlens_small.b2rs"))
+        img, names, secs = refrun.render_channels(pbrt)
+        np.save(os.path.join(out, "omni_microlens_small_ref.npy"), img.astype(np.float32))
+        print("omni_microlens_small", img.shape, "mean", img[..., :3].mean(axis=(0, 1)), f"{secs:.2f}s")
 
 
 # BASELINE.json configs[4] (scenes.config5_pbrt): VolPathIntegrator, homogeneous fog + a grid medium inside an
@@ -195,6 +201,10 @@ if __name__ == "__main__":
     import pbrt_v4_b200 as P
     import refrun
     out = os.path.dirname(os.path.abspath(__file__))
+    known = ("--omni-only", "--config4-only", "--config5-only", "--render-only")
+    for a in sys.argv[1:]:
+        if a not in known and not a.startswith("--only="):
+            sys.exit(f"unknown argument {a}; known: {known}, --only=name,...  (no argument regenerates every fixture)")
     if any(a.startswith("--only=") for a in sys.argv):
         pass
     elif "--config5-only" in sys.argv:

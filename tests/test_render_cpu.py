@@ -173,6 +173,31 @@ def test_golden_image_omni_camera(P, rendercheck):
     assert rrmse(img0, ref[..., :3]) > 100 * TOL_RRMSE
 
 
+def test_golden_image_omni_camera_microlens(P, rendercheck):
+    """SURVEY a17, second half: a microlens array in front of the sensor (TraceFullLensSystemFromFilm,
+    SampleMicrolensPupil, MicrolensElementFromIndex, TToBackLens; cameras.cpp:3259-3327, 3167-3187, 3221-3244,
+    2594-2611) with per-lens centre offsets.  The reference's constructor leaves microlens.simulationRadius at
+    the value of a not yet initialised member (cameras.cpp:2530): the dump carries what the object really held (0)."""
+    name = "omni_microlens_small"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    assert int(rsc.d["camera_type"][0]) == 2 and len(rsc.d["microlens_offsets"]) == 24 * 24
+    rgbw, bsum, wsum = rendercheck(rsc, full=True)
+    img = P.render.film_to_image(rgbw, rsc.d["film_matrix"])
+    assert rrmse(img, ref[..., :3]) <= TOL_RRMSE
+    assert abs(img.mean() - ref[..., :3].mean()) <= TOL_MEAN * ref[..., :3].mean()
+    spec = np.where(wsum > 0, bsum / np.where(wsum > 0, wsum, 1), 0).astype(np.float32).transpose(1, 2, 0)
+    assert rrmse(spec, ref[..., 3:]) <= TOL_RRMSE
+    d = dict(rsc.d)
+    d["microlens_offsets"] = rsc.d["microlens_offsets"] * 0  # the per-lens offsets have to matter
+    img0 = P.render.film_to_image(rendercheck(P.RenderScene(d)), rsc.d["film_matrix"])
+    assert rrmse(img0, ref[..., :3]) > 100 * TOL_RRMSE
+    d = dict(rsc.d)
+    d["microlens_ints"] = np.array([24, 24, 1], np.int32)  # 3 x 3 candidate lenses per ray: runs, image stays finite
+    img1 = P.render.film_to_image(rendercheck(P.RenderScene(d)), rsc.d["film_matrix"])
+    assert np.isfinite(img1).all() and img1.mean() > 0
+
+
 def test_realistic_camera_description_is_validated(P, rendercheck):
     rsc = P.RenderScene.load(os.path.join(GOLD, "config4_small.b2rs"))
     d = dict(rsc.d)

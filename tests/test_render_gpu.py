@@ -179,7 +179,7 @@ def test_spectral_image_needs_a_spectral_film(P, cornell):
         r.close()
 
 
-@pytest.mark.parametrize("name", ["config4_small", "omni_small"])
+@pytest.mark.parametrize("name", ["config4_small", "omni_small", "omni_microlens_small"])
 def test_config4_realistic_camera_spectral(P, rendercheck, name):
     """BASELINE configs[3] in miniature on the device: RealisticCamera rays + 31-band SpectralFilm against the
     reference's Film::GetImage, and against the CPU loop over the same headers.  omni_small: the same scene through
