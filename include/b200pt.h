@@ -65,11 +65,16 @@ typedef struct b200pt_mesh {
     const int32_t *indices; /* 3 per triangle; 4 per bilinear patch: p00 p10 p01 p11 */
     /* 0 = triangle mesh; 1 = bilinear patch mesh (BilinearPatchMesh, util/mesh.h:47-77; BilinearPatch::Intersect
      * / IntersectP, shapes.cpp:1131-1156 over IntersectBilinearPatch, shapes.h:1279-1347).  Hits on a patch report
-     * prim = the patch index and (b1, b2) = the patch's (u, v).  The traversal entry points take both kinds; the
-     * render path (b200pt_render_create) takes triangle meshes only so far. */
+     * prim = the patch index and (b1, b2) = the patch's (u, v).  Both the traversal entry points and the render
+     * path take both kinds.
+     * | B200PT_MESH_ALPHA (triangle meshes only): every primitive of the mesh carries the constant alpha texture
+     * `alpha` (GeometricPrimitive::Intersect / IntersectP, cpu/primitive.cpp:50-109): a hit counts when alpha >= 1, or
+     * alpha > 0 and HashFloat(ray.o, ray.d) <= alpha (the ray as the primitive receives it: the instance-space ray
+     * inside an object instance); otherwise the primitive is passed over.  `alpha` is read only under that flag. */
     uint32_t kind;
+    float alpha;
 } b200pt_mesh;
-enum { B200PT_MESH_TRIANGLES = 0, B200PT_MESH_BILINEAR = 1 };
+enum { B200PT_MESH_TRIANGLES = 0, B200PT_MESH_BILINEAR = 1, B200PT_MESH_ALPHA = 2 };
 
 /* One object instance (TransformedPrimitive, cpu/primitive.cpp:112-131).
  * instanceId reported in hits = 1 + index in instances[] (scene.cpp:1560-1573). */

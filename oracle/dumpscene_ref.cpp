@@ -430,6 +430,7 @@ int main(int argc, char **argv) {
     std::vector<int32_t> meshObject(nMesh, -1);
     // one triangle primitive of the world or of an object definition -> its mesh / material / light records
     std::map<int, std::pair<int, int>> meshMediaOf;  // reference mesh index -> {inside, outside}
+    std::map<int, float> meshAlphaOf;                // reference mesh index -> constant alpha
     auto visitTriangle = [&](const Primitive &p, int object, std::vector<uint32_t> &primsOut) {
         Shape shape;
         pbrt::Material mtl;
@@ -441,7 +442,13 @@ int main(int argc, char **argv) {
             shape = gp->shape;
             mtl = gp->material;
             area = gp->areaLight;
-            if (gp->alpha) die("alpha textures are not dumped");
+            if (gp->alpha) {  // constant alpha only: one value per mesh (the cut-out test runs inside traversal)
+                const FloatConstantTexture *ct = gp->alpha.CastOrNullptr<FloatConstantTexture>();
+                if (!ct || !shape.Is<Triangle>()) die("only constant alpha textures on triangle meshes are dumped");
+                int am = shape.Cast<Triangle>()->meshIndex;
+                if (meshAlphaOf.count(am) && meshAlphaOf[am] != ct->Evaluate(TextureEvalContext())) die("two alpha values on one mesh");
+                meshAlphaOf[am] = ct->Evaluate(TextureEvalContext());
+            }
             if (volpath && gp->mediumInterface.IsMediumTransition()) {
                 int mm = shape.Is<Triangle>() ? shape.Cast<Triangle>()->meshIndex
                                               : int(nTriMeshes) + shape.Cast<BilinearPatch>()->meshIndex;
@@ -617,6 +624,12 @@ int main(int argc, char **argv) {
     }
     w.i32("mesh_attr", {uint32_t(nMesh), 3}, meshAttr);
     w.i32("mesh_object", {uint32_t(nMesh)}, meshObject);
+    if (!meshAlphaOf.empty()) {  // -1 = no alpha texture
+        std::vector<float> ma(nMesh, -1.f);
+        for (auto &kv : meshAlphaOf)
+            if (meshRemap[kv.first] >= 0) ma[meshRemap[kv.first]] = kv.second;
+        w.f32("mesh_alpha", {uint32_t(nMesh)}, ma);
+    }
     if (volpath) {
         std::vector<int32_t> mm(nMesh * 2, -1);
         for (auto &kv : meshMediaOf)

@@ -50,6 +50,7 @@
 #include <pbrt/materials.h>
 #include <pbrt/options.h>
 #include <pbrt/shapes.h>
+#include <pbrt/textures.h>
 #include <pbrt/util/mesh.h>
 #include <pbrt/util/parallel.h>
 #include <pbrt/util/transform.h>
@@ -116,6 +117,11 @@ static Scene loadScene(const char *fn) {
         if (fread(&object, 4, 1, f) != 1 || fread(&nv, 4, 1, f) != 1 || fread(&nt, 4, 1, f) != 1 ||
             fread(&kind, 4, 1, f) != 1)
             die("short read");
+        // kind | 2: the mesh's primitives are GeometricPrimitives with a constant alpha texture (cpu/primitive.cpp:50-109)
+        float alpha = 1.f;
+        const bool hasAlpha = (kind & 2) != 0;
+        if (hasAlpha && fread(&alpha, 4, 1, f) != 1) die("short read");
+        kind &= 1;
         std::vector<float> P = readVec<float>(f, 3 * size_t(nv));
         std::vector<int> idx = readVec<int>(f, (kind == 1 ? 4 : 3) * size_t(nt));
         std::vector<Point3f> p(nv);
@@ -136,8 +142,13 @@ static Scene loadScene(const char *fn) {
             identity, false, std::move(idx), std::move(p), std::vector<Vector3f>(),
             std::vector<Normal3f>(), std::vector<Point2f>(), std::move(face), alloc);
         pstd::vector<Shape> tris = Triangle::CreateTriangles(mesh, alloc);
-        for (Shape s : tris)
-            dst.push_back(new SimplePrimitive(s, meshMaterial(m)));
+        for (Shape s : tris) {
+            if (hasAlpha)
+                dst.push_back(new GeometricPrimitive(s, meshMaterial(m), nullptr, MediumInterface(),
+                                                     FloatTexture(alloc.new_object<FloatConstantTexture>(alpha))));
+            else
+                dst.push_back(new SimplePrimitive(s, meshMaterial(m)));
+        }
     }
     Scene sc;
     sc.bvhs.push_back(nullptr);
@@ -215,6 +226,9 @@ static void dumpBVH(const Scene &sc, const char *out) {
                     rec[2] = bp->blpIndex;
                 } else
                     rec[2] = sp->shape.Cast<Triangle>()->triIndex;
+            } else if (const GeometricPrimitive *gp = p.CastOrNullptr<GeometricPrimitive>()) {
+                rec[1] = meshOfMaterial(gp->material);
+                rec[2] = gp->shape.Cast<Triangle>()->triIndex;
             } else if (const TransformedPrimitive *tp = p.CastOrNullptr<TransformedPrimitive>()) {
                 rec[0] = 1;
                 rec[1] = tp->instanceId;

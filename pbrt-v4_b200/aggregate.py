@@ -32,7 +32,7 @@ class B200Aggregate:
             idx = np.ascontiguousarray(m.indices, dtype=np.int32)
             self._keep += [p, idx]
             meshes[k] = capi.Mesh(int(m.object), p.shape[0], idx.shape[0], capi.fptr(p),
-                                  idx.ctypes.data_as(C.POINTER(C.c_int32)), int(getattr(m, "kind", 0)))
+                                  idx.ctypes.data_as(C.POINTER(C.c_int32)), *capi.mesh_kind_alpha(m))
         insts = (capi.Instance * max(1, len(scene.instances)))()
         for k, i in enumerate(scene.instances):
             insts[k].object = int(i.object)

@@ -22,7 +22,17 @@ assert HIT_DTYPE.itemsize == 24 and NODE32_DTYPE.itemsize == 32
 
 class Mesh(C.Structure):
     _fields_ = [("object", C.c_int32), ("n_vertices", C.c_uint32), ("n_triangles", C.c_uint32),
-                ("p", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_int32)), ("kind", C.c_uint32)]
+                ("p", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_int32)), ("kind", C.c_uint32),
+                ("alpha", C.c_float)]  # read under kind & MESH_ALPHA only
+
+
+MESH_TRIANGLES, MESH_BILINEAR, MESH_ALPHA = 0, 1, 2
+
+
+def mesh_kind_alpha(m):
+    """(kind word, alpha) of a scenes.Mesh for the C struct."""
+    a = getattr(m, "alpha", None)
+    return int(getattr(m, "kind", 0)) | (MESH_ALPHA if a is not None else 0), float(a if a is not None else 1.0)
 
 
 class Instance(C.Structure):

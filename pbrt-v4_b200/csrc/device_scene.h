@@ -19,7 +19,7 @@ struct alignas(32) PrimSlot {
     uint32_t tri;
     uint32_t flags;
     float p3[3];
-    uint32_t kind;  // 0 triangle (or instance), 1 bilinear patch
+    uint32_t kind;  // 0 triangle (or instance), 1 bilinear patch, 2 triangle with a constant alpha cut-out (alpha in p3[0])
 };
 static_assert(sizeof(PrimSlot) == 64, "PrimSlot is one 32-byte and one 16-byte load");
 constexpr uint32_t kInstanceTag = 0xFFFFFFFEu;

@@ -356,4 +356,34 @@ B2_HD bool BilinearHit(const RayCtx &r, float tMax, const float *p00, const floa
     return true;
 }
 
+// ---- alpha cut-outs: GeometricPrimitive::Intersect / IntersectP (cpu/primitive.cpp:50-109) with a constant alpha
+// texture.  A hit on a primitive with alpha a < 1 counts when a > 0 and HashFloat(r.o, r.d) <= a; otherwise the
+// reference re-traces the SAME shape from the hit point, which a planar triangle cannot meet again, so the primitive is
+// passed over.  HashFloat(o, d) = uint32(MurmurHash64A of the 24 argument bytes) * 2^-32 (util/hash.h:18-68, 95-110).
+B2_HD float HashFloatRay(const RayCtx &r) {
+    const float v[6] = {r.ox, r.oy, r.oz, r.dx, r.dy, r.dz};
+    const uint64_t m = 0xc6a4a7935bd1e995ull;
+    uint64_t h = 0 ^ (24ull * m);
+    for (int i = 0; i < 3; ++i) {
+        uint32_t lo, hi;
+        memcpy(&lo, &v[2 * i], 4);
+        memcpy(&hi, &v[2 * i + 1], 4);
+        uint64_t k = uint64_t(lo) | (uint64_t(hi) << 32);
+        k *= m;
+        k ^= k >> 47;
+        k *= m;
+        h ^= k;
+        h *= m;
+    }
+    h ^= h >> 47;
+    h *= m;
+    h ^= h >> 47;
+    return float(uint32_t(h)) * 0x1p-32f;
+}
+B2_HD bool AlphaKeepsHit(const RayCtx &r, float alpha) {
+    if (!(alpha < 1)) return true;
+    if (alpha <= 0) return false;
+    return !(HashFloatRay(r) > alpha);
+}
+
 }  // namespace b200pt

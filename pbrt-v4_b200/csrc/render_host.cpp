@@ -232,7 +232,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("mesh medium index out of range");
         }
         uint32_t nOff = kNoCornerAttr, uvOff = kNoCornerAttr;
-        if (meshKind[i] == 0 && (m.corner_n || m.corner_uv)) {
+        if ((meshKind[i] & 1) == 0 && (m.corner_n || m.corner_uv)) {
             if (out.cornerAttr.size() + 15 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
             if (m.corner_n) {
                 nOff = uint32_t(out.cornerAttr.size());

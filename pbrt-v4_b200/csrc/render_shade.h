@@ -138,7 +138,7 @@ template <int EXT = 1>
 B2_HD SurfHit SlotInteraction(const void *prims, uint32_t slot, const TriVerts &t, float b0, float b1, float b2, V3 wo,
                               bool flipNormal, CornerAttr ca) {
     if (EXT == 0) return TriangleInteraction(t, b0, b1, b2, wo, flipNormal);
-    if (t.kind == 1) {
+    if (t.kind & 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
         return PatchInteraction(pv, b1, b2, wo, flipNormal);
     }
@@ -665,7 +665,7 @@ template <int EXT = 1>
 B2_HD ShapeSampleOut SampleShapeSolidAngle(const void *prims, uint32_t slot, const TriVerts &t, const LightCtx &ctx, float u0,
                                            float u1, bool flipNormal, const float *cn) {
     if (EXT == 0) return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal);
-    if (t.kind == 1) {
+    if (t.kind & 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
         return SamplePatchSolidAngle(pv, ctx, u0, u1, flipNormal);
     }
@@ -674,7 +674,7 @@ B2_HD ShapeSampleOut SampleShapeSolidAngle(const void *prims, uint32_t slot, con
 template <int EXT = 1>
 B2_HD float ShapePDF(const void *prims, uint32_t slot, const TriVerts &t, const LightCtx &ctx, V3 wi, bool flipNormal) {
     if (EXT == 0) return TrianglePDF(t, ctx, wi, flipNormal);
-    if (t.kind == 1) {
+    if (t.kind & 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
         return PatchPDF(pv, ctx, wi, flipNormal);
     }

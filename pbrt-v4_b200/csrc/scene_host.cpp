@@ -32,7 +32,7 @@ inline Box PatchBox(const float *p00, const float *p10, const float *p01, const 
 }
 // box and BVH record of primitive i of a mesh of either kind
 inline Box MeshPrimBox(const b200pt_mesh &mesh, uint32_t i) {
-    if (mesh.kind == B200PT_MESH_BILINEAR) {
+    if (mesh.kind & B200PT_MESH_BILINEAR) {
         const int32_t *v = mesh.indices + 4ull * i;
         return PatchBox(mesh.p + 3ull * v[0], mesh.p + 3ull * v[1], mesh.p + 3ull * v[2], mesh.p + 3ull * v[3]);
     }
@@ -96,17 +96,22 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             err = "mesh with null arrays";
             return B200PT_ERR_INVALID;
         }
-        if (mesh.kind > B200PT_MESH_BILINEAR) {
-            err = "unknown mesh kind";
+        if (mesh.kind > (B200PT_MESH_BILINEAR | B200PT_MESH_ALPHA) || mesh.kind == (B200PT_MESH_BILINEAR | B200PT_MESH_ALPHA)) {
+            err = "unknown mesh kind (alpha cut-outs: triangle meshes only)";
             return B200PT_ERR_INVALID;
         }
-        const uint64_t perPrim = mesh.kind == B200PT_MESH_BILINEAR ? 4 : 3;
+        if ((mesh.kind & B200PT_MESH_ALPHA) && !(mesh.alpha == mesh.alpha)) {
+            err = "mesh alpha is NaN";
+            return B200PT_ERR_INVALID;
+        }
+        const uint64_t perPrim = (mesh.kind & B200PT_MESH_BILINEAR) ? 4 : 3;
         for (uint64_t i = 0; i < perPrim * mesh.n_triangles; ++i)
             if (mesh.indices[i] < 0 || uint32_t(mesh.indices[i]) >= mesh.n_vertices) {
                 err = "vertex index out of range";
                 return B200PT_ERR_INVALID;
             }
-        if (mesh.kind == B200PT_MESH_BILINEAR && mesh.n_triangles) out.hasPatches = true;
+        // patches and alpha triangles use the slots' last 16 bytes: the kernels' extended-slot variant
+        if ((mesh.kind & (B200PT_MESH_BILINEAR | B200PT_MESH_ALPHA)) && mesh.n_triangles) out.hasPatches = true;
         objMeshes[mesh.object < 0 ? -1 : mesh.object].push_back(m);
         nTri += mesh.n_triangles;
     }
@@ -169,7 +174,7 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                 const b200pt_mesh &mesh = desc->meshes[m];
                 for (uint32_t i = 0; i < mesh.n_triangles; ++i) {
                     ob.push_back(MeshPrimBox(mesh, i));
-                    orf.push_back({mesh.kind == B200PT_MESH_BILINEAR ? 2u : 0u, m, i});
+                    orf.push_back({(mesh.kind & B200PT_MESH_BILINEAR) ? 2u : 0u, m, i});
                 }
             }
             if (ob.empty()) {
@@ -197,7 +202,7 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             const b200pt_mesh &mesh = desc->meshes[m];
             for (uint32_t i = 0; i < mesh.n_triangles; ++i) {
                 boxes.push_back(MeshPrimBox(mesh, i));
-                refs.push_back({mesh.kind == B200PT_MESH_BILINEAR ? 2u : 0u, m, i});
+                refs.push_back({(mesh.kind & B200PT_MESH_BILINEAR) ? 2u : 0u, m, i});
             }
         }
         for (uint32_t i = 0; i < desc->n_instances; ++i) {
@@ -259,7 +264,7 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                     PrimSlot s;
                     std::memset(&s, 0, sizeof s);
                     if (pr[0] == 2) {
-                        if (pr[1] >= desc->n_meshes || desc->meshes[pr[1]].kind != B200PT_MESH_BILINEAR ||
+                        if (pr[1] >= desc->n_meshes || !(desc->meshes[pr[1]].kind & B200PT_MESH_BILINEAR) ||
                             pr[2] >= desc->meshes[pr[1]].n_triangles) {
                             err = "bvh primitive refers to a missing bilinear patch";
                             return B200PT_ERR_INVALID;
@@ -274,7 +279,7 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                         s.tri = pr[2];
                         s.kind = 1;
                     } else if (pr[0] == 0) {
-                        if (pr[1] >= desc->n_meshes || desc->meshes[pr[1]].kind != B200PT_MESH_TRIANGLES ||
+                        if (pr[1] >= desc->n_meshes || (desc->meshes[pr[1]].kind & B200PT_MESH_BILINEAR) ||
                             pr[2] >= desc->meshes[pr[1]].n_triangles) {
                             err = "bvh primitive refers to a missing triangle";
                             return B200PT_ERR_INVALID;
@@ -286,6 +291,10 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
                         std::memcpy(s.p2, mesh.p + 3ull * v[2], 12);
                         s.mesh = pr[1];
                         s.tri = pr[2];
+                        if (mesh.kind & B200PT_MESH_ALPHA) {  // constant alpha rides in the unused fourth corner
+                            s.kind = 2;
+                            s.p3[0] = mesh.alpha;
+                        }
                     } else if (pr[0] == 1 && t.object == -1) {
                         if (pr[1] < 1 || pr[1] > desc->n_instances) {
                             err = "bvh primitive refers to a missing instance";

@@ -69,8 +69,10 @@ TraverseBVH2Kernel(DeviceScene sc, const float *__restrict__ rays, long long n,
                         if (sc.hasPatches) {
                             float4 d4 = __ldg(prims + 4 * slot + 3);
                             float p3[3] = {d4.x, d4.y, d4.z};
-                            primHit = __float_as_uint(d4.w) == 1u ? BilinearHit(r, tMax, p0, p1, p2, p3, t, b1, b2)
-                                                                  : TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
+                            const uint32_t kind = __float_as_uint(d4.w);
+                            primHit = (kind & 1u) ? BilinearHit(r, tMax, p0, p1, p2, p3, t, b1, b2)
+                                                  : TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
+                            if (primHit && (kind & 2u)) primHit = AlphaKeepsHit(r, d4.x);
                         } else
                             primHit = TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
                         if (primHit) {

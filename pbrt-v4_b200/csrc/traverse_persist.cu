@@ -235,12 +235,15 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                 bool primHit;
                 if (PATCH) {
                     float4 c4 = __ldg(reinterpret_cast<const float4 *>(prims + 64ll * slot + 48));
-                    if (__float_as_uint(c4.w) == 1u) {  // p0..p3 = p00, p10, p01, p11
+                    const uint32_t kind = __float_as_uint(c4.w);
+                    if (kind & 1u) {  // p0..p3 = p00, p10, p01, p11
                         float p3[3] = {c4.x, c4.y, c4.z};
                         b0 = 0.f;
                         primHit = BilinearHit(r, tMax, p0, p1, p2, p3, t, b1, b2);
-                    } else
+                    } else {
                         primHit = TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
+                        if (primHit && (kind & 2u)) primHit = AlphaKeepsHit(r, c4.x);  // alpha cut-out triangle
+                    }
                 } else
                     primHit = TriHit(r, tMax, p0, p1, p2, t, b0, b1, b2);
                 if (primHit) {

@@ -23,7 +23,8 @@ class RenderScene:
         obj = d["mesh_object"] if "mesh_object" in d else np.full(len(nv), -1, np.int32)
         meshes = [scenes.Mesh(d["P"][vo[i]:vo[i + 1]],
                               d["patch_indices"][po[i]:po[i + 1]] if kind[i] else d["indices"][to[i]:to[i + 1]],
-                              object=int(obj[i]), kind=int(kind[i]))
+                              object=int(obj[i]), kind=int(kind[i]),
+                              alpha=(float(d["mesh_alpha"][i]) if "mesh_alpha" in d and d["mesh_alpha"][i] >= 0 else None))
                   for i in range(len(nv))]
         insts = []
         if "instance_object" in d:
@@ -188,7 +189,7 @@ def scene_desc(geometry, bvh, keep):
         p, idx = np.ascontiguousarray(m.p, np.float32), np.ascontiguousarray(m.indices, np.int32)
         keep += [p, idx]
         meshes[k] = capi.Mesh(int(m.object), p.shape[0], idx.shape[0], capi.fptr(p),
-                              idx.ctypes.data_as(C.POINTER(C.c_int32)), int(getattr(m, "kind", 0)))
+                              idx.ctypes.data_as(C.POINTER(C.c_int32)), *capi.mesh_kind_alpha(m))
     barr = (capi.BVH2 * max(1, len(bvh) if bvh else 1))()
     nb = 0
     if bvh:

@@ -4,7 +4,8 @@ the product (through capi / B200Aggregate) and the reference driver
 (oracle/raycast_ref.cpp).  numpy only; nothing here computes intersections.
 
 File layout:  u32 magic 'B2SC', u32 version=2, u32 nMeshes, u32 nInstances
-  per mesh:     i32 object (-1 world), u32 nVerts, u32 nPrims, u32 kind (0 triangles, 1 bilinear patches),
+  per mesh:     i32 object (-1 world), u32 nVerts, u32 nPrims, u32 kind (0 triangles, 1 bilinear patches; | 2: an
+                f32 constant alpha follows),
                 f32 P[3nV], i32 idx[(3 or 4) nPrims]
   per instance: u32 object, f32 renderFromInstance[16], f32 instanceFromRender[16]
 """
@@ -24,6 +25,7 @@ class Mesh:
     indices: np.ndarray      # (nt, 3) int32; bilinear patches: (np, 4) = p00 p10 p01 p11
     object: int = -1         # -1: world; >= 0: object definition id
     kind: int = 0            # 0 triangles, 1 bilinear patches
+    alpha: float = None      # constant alpha cut-out of a triangle mesh (None: opaque, no alpha texture)
 
     def __post_init__(self):
         self.p = np.ascontiguousarray(self.p, dtype=np.float32).reshape(-1, 3)
@@ -55,7 +57,9 @@ class Scene:
             np.array([MAGIC, 2, len(self.meshes), len(self.instances)], dtype="<u4").tofile(f)
             for m in self.meshes:
                 np.array([m.object], dtype="<i4").tofile(f)
-                np.array([m.p.shape[0], m.indices.shape[0], m.kind], dtype="<u4").tofile(f)
+                np.array([m.p.shape[0], m.indices.shape[0], m.kind | (2 if m.alpha is not None else 0)], dtype="<u4").tofile(f)
+                if m.alpha is not None:
+                    np.array([m.alpha], dtype="<f4").tofile(f)
                 m.p.astype("<f4").tofile(f)
                 m.indices.astype("<i4").tofile(f)
             for i in self.instances:
@@ -162,6 +166,20 @@ def patch_scene(n_patches=20000, n_tris=10000, seed=91, s=0.03):
     if n_tris:
         meshes.append(random_soup(n_tris, seed=seed + 1, s=s).meshes[0])
     return Scene(meshes)
+
+
+def alpha_scene(seed=43):
+    """Alpha cut-outs at every level: an instanced scene whose world mesh and one object mesh carry a
+    constant alpha in (0, 1) (stochastic cut-out by HashFloat(ray.o, ray.d), the instance-space ray inside objects),
+    plus world soups with alpha 0 (never hit), alpha 1 (opaque through the GeometricPrimitive path) and none."""
+    sc = instanced_scene(n_objects=3, tris_per_object=500, n_instances=20, world_tris=1200, seed=seed)
+    world = [m for m in sc.meshes if m.object < 0]
+    objs = [m for m in sc.meshes if m.object >= 0]
+    world[0].alpha = 0.6
+    objs[0].alpha = 0.35
+    extra = random_soup(1500, seed=seed + 1, s=0.04, n_meshes=3).meshes
+    extra[0].alpha, extra[1].alpha = 0.0, 1.0
+    return Scene(sc.meshes + extra, sc.instances)
 
 
 def _quad(p0, p1, p2, p3):

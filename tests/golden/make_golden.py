@@ -20,7 +20,10 @@ def cases(S):
     sheet = S.Scene([S.grid_sheet(32, 32, jitter=0.0), S.grid_sheet(24, 24, z=0.75, jitter=0.02, seed=9)])
     inst = S.instanced_scene(n_objects=3, tris_per_object=600, n_instances=24, world_tris=1500, seed=41)
     patches = S.patch_scene(6000, 3000, seed=95)
+    alpha = S.alpha_scene(seed=43)
     return {
+        "alpha_primary": (alpha, S.primary_rays(30000, seed=44)),
+        "alpha_adversarial": (alpha, S.adversarial_rays(S.flattened(alpha), 20000, seed=45)),
         "patches_primary": (patches, S.primary_rays(30000, seed=38)),
         "patches_adversarial": (patches, S.adversarial_rays(patches, 20000, seed=39)),
         "instanced_primary": (inst, S.primary_rays(30000, seed=36)),

@@ -48,8 +48,9 @@ static bool TraceNodes(const HostScene &hs, int root, bool testRoot, const float
                     }
                     float t, b0, b1, b2;
                     b0 = 0;
-                    if (s.kind == 1 ? BilinearHit(r, tMax, s.p0, s.p1, s.p2, s.p3, t, b1, b2)
-                                    : TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
+                    if (((s.kind & 1) ? BilinearHit(r, tMax, s.p0, s.p1, s.p2, s.p3, t, b1, b2)
+                                      : TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) &&
+                        (!(s.kind & 2) || AlphaKeepsHit(r, s.p3[0]))) {
                         if (any) return true;
                         tMax = t; best.slot = nd.offset + k; best.inst = curInst; best.b1 = b1; best.b2 = b2;
                     }
@@ -84,10 +85,12 @@ int main(int argc, char **argv) {
         int32_t obj; uint32_t nv, nt, kind;
         if (fread(&obj, 4, 1, f) != 1 || fread(&nv, 4, 1, f) != 1 || fread(&nt, 4, 1, f) != 1 || fread(&kind, 4, 1, f) != 1)
             return 2;
-        P[m].resize(3 * size_t(nv)); I[m].resize((kind == 1 ? 4 : 3) * size_t(nt));
+        float alpha = 1.f;
+        if ((kind & 2) && fread(&alpha, 4, 1, f) != 1) return 2;
+        P[m].resize(3 * size_t(nv)); I[m].resize(((kind & 1) ? 4 : 3) * size_t(nt));
         if (fread(P[m].data(), 4, P[m].size(), f) != P[m].size()) return 2;
         if (fread(I[m].data(), 4, I[m].size(), f) != I[m].size()) return 2;
-        meshes[m] = b200pt_mesh{obj, nv, nt, P[m].data(), I[m].data(), kind};
+        meshes[m] = b200pt_mesh{obj, nv, nt, P[m].data(), I[m].data(), kind, alpha};
     }
     std::vector<b200pt_instance> insts(hdr[3]);
     for (uint32_t i = 0; i < hdr[3]; ++i) {

@@ -70,8 +70,9 @@ inline bool TracePairs(const HostScene &hs, int rootRef, const float *rootBox, c
                 }
                 float t, b0, b1, b2;
                 b0 = 0;
-                    if (s.kind == 1 ? BilinearHit(r, tMax, s.p0, s.p1, s.p2, s.p3, t, b1, b2)
-                                    : TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) {
+                    if (((s.kind & 1) ? BilinearHit(r, tMax, s.p0, s.p1, s.p2, s.p3, t, b1, b2)
+                                      : TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) &&
+                        (!(s.kind & 2) || AlphaKeepsHit(r, s.p3[0]))) {
                     if (any) return true;
                     tMax = t; best.slot = slot; best.inst = curInst; best.b0 = b0; best.b1 = b1; best.b2 = b2;
                 }

@@ -16,7 +16,8 @@ _spec = importlib.util.spec_from_file_location("make_golden", os.path.join(ROOT,
 G = importlib.util.module_from_spec(_spec)
 _spec.loader.exec_module(G)
 NAMES = ["soup20k_primary", "soup20k_adversarial", "cornell_camera", "cornell_adversarial", "sheets_adversarial",
-         "instanced_primary", "instanced_adversarial", "patches_primary", "patches_adversarial"]
+         "instanced_primary", "instanced_adversarial", "patches_primary", "patches_adversarial",
+         "alpha_primary", "alpha_adversarial"]
 
 
 @pytest.mark.parametrize("name", NAMES)
