@@ -359,7 +359,7 @@ MATERIALS = {
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
                  boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
-                 film="rgb", nbuckets=31, patches=False, smooth=False):
+                 film="rgb", nbuckets=31, patches=False, smooth=False, alpha=False):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -411,7 +411,8 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
                 continue
         else:
             lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
-        lines.append('  ' + _mesh_pbrt(m))
+        # alpha: the tall box is a stochastic cut-out (constant alpha 0.5), cpu/primitive.cpp:57-70
+        lines.append('  ' + _mesh_pbrt(m) + (' "float alpha" 0.5' if alpha and k == 6 else ''))
         lines.append('AttributeEnd')
     if many_lights:
         # config 3's "many-light" mechanism at test size: small one-sided emissive quads of varied power,
@@ -447,6 +448,14 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
                   'AttributeBegin', '  ' + MATERIALS["conductor_rough"], '  ReverseOrientation',
                   '  ' + sheet(0.05, 0.3, 0.1, 0.45, 1, lambda u, v: 0.75 + 0.18 * (2 * u - 1) * (2 * v - 1)),
                   'AttributeEnd']
+    if alpha:
+        # a 30 % screen in front of the camera and a fully cut-out (alpha 0) blocker under the light
+        lines += ['AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.2 0.7 0.3]',
+                  '  Shape "trianglemesh" "point3 P" [0.2 0.2 0.05  0.8 0.2 0.05  0.8 0.8 0.1  0.2 0.8 0.1] '
+                  '"integer indices" [0 1 2 0 2 3] "float alpha" 0.3', 'AttributeEnd',
+                  'AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.9 0.1 0.1]',
+                  '  Shape "trianglemesh" "point3 P" [0.3 0.9 0.3  0.7 0.9 0.3  0.7 0.9 0.7  0.3 0.9 0.7] '
+                  '"integer indices" [0 1 2 0 2 3] "float alpha" 0', 'AttributeEnd']
     if smooth:
         # triangle meshes with per-vertex normals and uv (Triangle::InteractionFromIntersection's shading geometry,
         # shapes.h:934-1005): an anisotropic metal ball, a diffuse ball with normals only, and a small emissive

@@ -37,7 +37,8 @@ def _check(P, rendercheck, name, **kw):
                                   "cornell_metal2_r48_s8", "cornell_instanced_r64_s16", "cornell_manylights_r64_s16",
                                   "cornell_infinite_r64_s16", "cornell_infinite_power_r48_s8",
                                   "cornell_patches_r64_s16", "cornell_patchlights_r64_s16",  # bilinear patches, shaded and emissive
-                                  "cornell_smooth_r64_s16"])  # per-vertex normals + uv (shading geometry)
+                                  "cornell_smooth_r64_s16",  # per-vertex normals + uv (shading geometry)
+                                  "cornell_alpha_r64_s16"])  # constant alpha cut-outs
 def test_golden_image(P, rendercheck, name):
     _check(P, rendercheck, name)
 
