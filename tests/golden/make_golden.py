@@ -89,7 +89,11 @@ RENDER_CASES = {
 # reference; on the GPU the last-bit differences of CUDA's sinf/cosf flip a few such roulette tests.)
 # (coated: the layered BxDF's random walk is carried as a polynomial in R_k here, csrc/render_layered.h, so its
 # internal roulette tests see max_k beta_k with different rounding: most walks are the reference's, a few are not.)
-NOISE_GATED = {"cornell_glass_r64_s16", "cornell_metal2_r48_s8", "cornell_coated_r64_s16"}
+# (alpha: the cut-out decision hashes the ray's bits, HashFloat(ray.o, ray.d); on the CPU check every ray has the
+# reference's bits and the image agrees to 6e-6, on the GPU a last-bit difference of sinf / cosf in a sampled direction
+# flips decisions further down the path.  The decisions themselves are pinned bit for bit on given rays by the
+# alpha_primary / alpha_adversarial traversal fixtures, on the GPU too.)
+NOISE_GATED = {"cornell_glass_r64_s16", "cornell_metal2_r48_s8", "cornell_coated_r64_s16", "cornell_alpha_r64_s16"}
 # scene tables only (no image): BASELINE.json configs[0] at full size, for bench.py and the
 # full-size GPU test, which render the reference image on the spot with oracle/_ref/pbrt_ref
 TABLE_CASES = {
