@@ -218,7 +218,9 @@ typedef struct b200pt_mesh_attr {
     uint32_t flip_normal; /* reverseOrientation ^ transformSwapsHandedness (util/mesh.h:42) */
     /* TriangleMesh::n / ::uv (util/mesh.h:44-47) of a triangle mesh, one entry per triangle CORNER in index order
      * (3 x 3 floats, 3 x 2 floats per triangle), or NULL: shading normals and the (u,v) parameterisation of
-     * Triangle::InteractionFromIntersection (shapes.h:884-1010).  Ignored for bilinear patch meshes. */
+     * Triangle::InteractionFromIntersection (shapes.h:884-1010).  A bilinear patch mesh takes corner_n with FOUR
+     * entries per patch (4 x 3 floats, index order p00 p10 p01 p11: BilinearPatchMesh::n, shapes.h:1474-1494);
+     * its corner_uv is ignored. */
     const float *corner_n;
     const float *corner_uv;
 } b200pt_mesh_attr;

@@ -580,13 +580,17 @@ int main(int argc, char **argv) {
         if (meshRemap[m] < 0) continue;
         if (m >= nTriMeshes) {
             const BilinearPatchMesh *mesh = patchMesh(m);
-            if (mesh->n || mesh->uv) fprintf(stderr, "dumpscene_ref: note: per-vertex n/uv of patch mesh %zu ignored\n", m);
+            if (mesh->uv) die("per-vertex uv on bilinear patch meshes is not dumped");
             if (mesh->imageDistribution) die("image-distributed patch emission is not dumped");
             nv.push_back(mesh->nVertices);
             nt.push_back(mesh->nPatches);
             meshKind.push_back(1);
-            meshHasN.push_back(0);
+            meshHasN.push_back(mesh->n ? 1 : 0);  // four corner normals per patch
             meshHasUV.push_back(0);
+            for (int i = 0; mesh->n && i < 4 * mesh->nPatches; ++i) {
+                const Normal3f &vn = mesh->n[mesh->vertexIndices[i]];
+                cornerN.insert(cornerN.end(), {vn.x, vn.y, vn.z});
+            }
             for (int i = 0; i < mesh->nVertices; ++i) P.insert(P.end(), {mesh->p[i].x, mesh->p[i].y, mesh->p[i].z});
             patchIdx.insert(patchIdx.end(), mesh->vertexIndices, mesh->vertexIndices + 4 * mesh->nPatches);
             continue;

@@ -232,13 +232,14 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("mesh medium index out of range");
         }
         uint32_t nOff = kNoCornerAttr, uvOff = kNoCornerAttr;
-        if ((meshKind[i] & 1) == 0 && (m.corner_n || m.corner_uv)) {
-            if (out.cornerAttr.size() + 15 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
+        if (m.corner_n || m.corner_uv) {
+            const bool patch = (meshKind[i] & 1) != 0;  // four corners per patch, normals only
+            if (out.cornerAttr.size() + 18 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
             if (m.corner_n) {
                 nOff = uint32_t(out.cornerAttr.size());
-                out.cornerAttr.insert(out.cornerAttr.end(), m.corner_n, m.corner_n + 9 * size_t(meshTris[i]));
+                out.cornerAttr.insert(out.cornerAttr.end(), m.corner_n, m.corner_n + (patch ? 12 : 9) * size_t(meshTris[i]));
             }
-            if (m.corner_uv) {
+            if (m.corner_uv && !patch) {
                 uvOff = uint32_t(out.cornerAttr.size());
                 out.cornerAttr.insert(out.cornerAttr.end(), m.corner_uv, m.corner_uv + 6 * size_t(meshTris[i]));
             }

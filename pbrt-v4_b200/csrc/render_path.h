@@ -296,10 +296,10 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
         V3 dInst = mk(mi[0] * p.rayD.x + mi[1] * p.rayD.y + mi[2] * p.rayD.z,
                       mi[4] * p.rayD.x + mi[5] * p.rayD.y + mi[6] * p.rayD.z,
                       mi[8] * p.rayD.x + mi[9] * p.rayD.y + mi[10] * p.rayD.z);
-        si = SlotInteraction<EXT>(rs.prims, slot, tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, slot, tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri, tv.kind));
         TransformSurfHit(in, si);
     } else {
-        si = SlotInteraction<EXT>(rs.prims, slot, tv, b0, b1, b2, wo, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, slot, tv, b0, b1, b2, wo, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri, tv.kind));
     }
 
     // ---- emitted light at the hit (cpu/integrators.cpp:664-679)
@@ -427,7 +427,7 @@ B2_SPECTRAL_LOOP
             ss.ok = false;
             if (lidx >= 0 && light.type == 0) {
                 TriVerts lt = LoadTri(rs.prims, light.slot);
-                ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, uLight0, uLight1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri).n);
+                ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, uLight0, uLight1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri, lt.kind).n);
             }
             V3 cp = Mid(ctx.pi);
             if (ss.ok && ss.pdf != 0 && LengthSquared(Mid(ss.pi) - cp) != 0) {

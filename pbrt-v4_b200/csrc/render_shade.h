@@ -44,9 +44,9 @@ struct SurfHit {
 struct CornerAttr {
     const float *n, *uv;
 };
-B2_HD CornerAttr CornersOf(const RenderSceneDev &rs, const MeshAttrDev &mesh, uint32_t tri) {
-    CornerAttr c;
-    c.n = mesh.nOff != kNoCornerAttr ? rs.cornerAttr + mesh.nOff + 9 * size_t(tri) : nullptr;
+B2_HD CornerAttr CornersOf(const RenderSceneDev &rs, const MeshAttrDev &mesh, uint32_t tri, uint32_t kind = 0) {
+    CornerAttr c;  // a bilinear patch has four corners (normals only)
+    c.n = mesh.nOff != kNoCornerAttr ? rs.cornerAttr + mesh.nOff + ((kind & 1) ? 12 : 9) * size_t(tri) : nullptr;
     c.uv = mesh.uvOff != kNoCornerAttr ? rs.cornerAttr + mesh.uvOff + 6 * size_t(tri) : nullptr;
     return c;
 }
@@ -112,7 +112,29 @@ B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b
 
 // BilinearPatch::InteractionFromIntersection (shapes.h:1396-1500) for meshes without per-vertex uv / n: the point and
 // both partial derivatives are lerps of the four corners at the hit's (u,v); the normal is their cross product.
-B2_HD_CALL SurfHit PatchInteraction(const PatchVerts &t, float u, float v, V3 wo, bool flipNormal) {
+// the interpolated vertex normal of a patch at (u, v): Lerp(u, Lerp(v, n00, n01), Lerp(v, n10, n11)), corners in index order
+B2_HD V3 PatchNormalAt(const float *cn, float u, float v) {
+    V3 n00 = mk(cn[0], cn[1], cn[2]), n10 = mk(cn[3], cn[4], cn[5]), n01 = mk(cn[6], cn[7], cn[8]), n11 = mk(cn[9], cn[10], cn[11]);
+    return (1 - u) * ((1 - v) * n00 + v * n01) + u * ((1 - v) * n10 + v * n11);
+}
+// RotateFromTo (util/transform.h:249-270) applied to a vector
+B2_HD void RotateFromTo(V3 from, V3 to, float r[3][3]) {
+    V3 refl;
+    if (fabsf(from.x) < 0.72f && fabsf(to.x) < 0.72f)
+        refl = mk(1, 0, 0);
+    else if (fabsf(from.y) < 0.72f && fabsf(to.y) < 0.72f)
+        refl = mk(0, 1, 0);
+    else
+        refl = mk(0, 0, 1);
+    V3 u = refl - from, v = refl - to;
+    const float uu[3] = {u.x, u.y, u.z}, vv[3] = {v.x, v.y, v.z};
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            r[i][j] = ((i == j) ? 1 : 0) - 2 / Dot(u, u) * uu[i] * uu[j] - 2 / Dot(v, v) * vv[i] * vv[j] +
+                      4 * Dot(u, v) / (Dot(u, u) * Dot(v, v)) * vv[i] * uu[j];
+}
+
+B2_HD_CALL SurfHit PatchInteraction(const PatchVerts &t, float u, float v, V3 wo, bool flipNormal, const float *cn = nullptr) {
     SurfHit h;
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     V3 e0 = (1 - v) * p00 + v * p01, e1 = (1 - v) * p10 + v * p11;
@@ -129,6 +151,18 @@ B2_HD_CALL SurfHit PatchInteraction(const PatchVerts &t, float u, float v, V3 wo
     h.ns = n;
     h.dpdus = dpdu;
     h.wo = Normalize(wo);
+    if (cn) {  // shading normal from the vertex normals (shapes.h:1474-1494), no per-vertex uv
+        V3 ns = PatchNormalAt(cn, u, v);
+        if (LengthSquared(ns) > 0) {
+            ns = Normalize(ns);
+            float r[3][3];
+            RotateFromTo(Normalize(h.n), ns, r);
+            h.dpdus = mk(r[0][0] * dpdu.x + r[0][1] * dpdu.y + r[0][2] * dpdu.z, r[1][0] * dpdu.x + r[1][1] * dpdu.y + r[1][2] * dpdu.z,
+                         r[2][0] * dpdu.x + r[2][1] * dpdu.y + r[2][2] * dpdu.z);
+            h.ns = ns;
+            h.n = FaceForward(h.n, ns);  // SetShadingGeometry(..., orientationIsAuthoritative = true)
+        }
+    }
     return h;
 }
 
@@ -140,7 +174,7 @@ B2_HD SurfHit SlotInteraction(const void *prims, uint32_t slot, const TriVerts &
     if (EXT == 0) return TriangleInteraction(t, b0, b1, b2, wo, flipNormal);
     if (t.kind & 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
-        return PatchInteraction(pv, b1, b2, wo, flipNormal);
+        return PatchInteraction(pv, b1, b2, wo, flipNormal, ca.n);
     }
     return TriangleInteraction(t, b0, b1, b2, wo, flipNormal, ca);
 }
@@ -508,7 +542,8 @@ B2_HD void PatchAreaWeights(const PatchVerts &t, float w[4]) {
 }
 
 // BilinearPatch::Sample(u) by area (shapes.cpp:1158-1217), no image distribution, no per-vertex uv / n
-B2_HD ShapeSampleOut SamplePatchArea(const PatchVerts &t, bool rectangle, float u0, float u1, bool flipNormal) {
+B2_HD ShapeSampleOut SamplePatchArea(const PatchVerts &t, bool rectangle, float u0, float u1, bool flipNormal,
+                                     const float *cn = nullptr) {
     ShapeSampleOut o;
     o.ok = false;
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
@@ -525,7 +560,10 @@ B2_HD ShapeSampleOut SamplePatchArea(const PatchVerts &t, bool rectangle, float 
     V3 dpdv = ((1 - su) * p01 + su * p11) - ((1 - su) * p00 + su * p10);
     if (LengthSquared(dpdu) == 0 || LengthSquared(dpdv) == 0) return o;
     V3 n = Normalize(Cross(dpdu, dpdv));
-    if (flipNormal) n = -n;
+    if (cn)
+        n = FaceForward(n, PatchNormalAt(cn, su, sv));
+    else if (flipNormal)
+        n = -n;
     V3 pAbsSum = Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11);
     o.pi = MakeP3i(p, GammaF(6) * pAbsSum);
     o.n = n;
@@ -544,13 +582,14 @@ B2_HD void PatchCosWeights(V3 v00, V3 v10, V3 v01, V3 v11, V3 ns, float w[4]) { 
 constexpr float kPatchMinSphericalSampleArea = 1e-4f;  // shapes.h:1538
 
 // BilinearPatch::Sample(ctx, u) (shapes.cpp:1257-1330)
-B2_HD_CALL ShapeSampleOut SamplePatchSolidAngle(const PatchVerts &t, const LightCtx &ctx, float u0, float u1, bool flipNormal) {
+B2_HD_CALL ShapeSampleOut SamplePatchSolidAngle(const PatchVerts &t, const LightCtx &ctx, float u0, float u1, bool flipNormal,
+                                                const float *cn = nullptr) {
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     V3 rp = Mid(ctx.pi);
     V3 v00 = Normalize(p00 - rp), v10 = Normalize(p10 - rp), v01 = Normalize(p01 - rp), v11 = Normalize(p11 - rp);
     bool rectangle = PatchIsRectangle(t);
     if (!rectangle || SphericalQuadArea(v00, v10, v11, v01) <= kPatchMinSphericalSampleArea) {
-        ShapeSampleOut o = SamplePatchArea(t, rectangle, u0, u1, flipNormal);
+        ShapeSampleOut o = SamplePatchArea(t, rectangle, u0, u1, flipNormal, cn);
         if (!o.ok) return o;
         V3 wi = Mid(o.pi) - rp;
         if (LengthSquared(wi) == 0) {
@@ -577,7 +616,11 @@ B2_HD_CALL ShapeSampleOut SamplePatchSolidAngle(const PatchVerts &t, const Light
     V3 p = SampleSphericalRectangle(rp, p00, eu, ev, u0, u1, &quadPDF);
     pdf *= quadPDF;
     V3 n = Normalize(Cross(eu, ev));
-    if (flipNormal) n = -n;
+    if (cn) {  // (u, v) of the sampled point on the rectangle (shapes.cpp:1306-1308)
+        float su = Dot(p - p00, eu) / LengthSquared(p10 - p00), sv = Dot(p - p00, ev) / LengthSquared(p01 - p00);
+        n = FaceForward(n, PatchNormalAt(cn, su, sv));
+    } else if (flipNormal)
+        n = -n;
     o.pi = MakeP3i(p, mk(0, 0, 0));
     o.n = n;
     o.pdf = pdf;
@@ -667,7 +710,7 @@ B2_HD ShapeSampleOut SampleShapeSolidAngle(const void *prims, uint32_t slot, con
     if (EXT == 0) return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal);
     if (t.kind & 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
-        return SamplePatchSolidAngle(pv, ctx, u0, u1, flipNormal);
+        return SamplePatchSolidAngle(pv, ctx, u0, u1, flipNormal, cn);
     }
     return SampleTriangleSolidAngle(t, ctx, u0, u1, flipNormal, cn);
 }

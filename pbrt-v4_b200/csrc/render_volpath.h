@@ -23,10 +23,10 @@ B2_HD SurfHit SurfHitFromRecord(const RenderSceneDev &rs, V3 rayD, const uint32_
         const float *mi = in.mInv;
         V3 dInst = mk(mi[0] * rayD.x + mi[1] * rayD.y + mi[2] * rayD.z, mi[4] * rayD.x + mi[5] * rayD.y + mi[6] * rayD.z,
                       mi[8] * rayD.x + mi[9] * rayD.y + mi[10] * rayD.z);
-        si = SlotInteraction<EXT>(rs.prims, hit[0], tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, hit[0], tv, b0, b1, b2, -dInst, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri, tv.kind));
         TransformSurfHit(in, si);
     } else {
-        si = SlotInteraction<EXT>(rs.prims, hit[0], tv, b0, b1, b2, -rayD, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri));
+        si = SlotInteraction<EXT>(rs.prims, hit[0], tv, b0, b1, b2, -rayD, mesh.flipNormal != 0, CornersOf(rs, mesh, tv.tri, tv.kind));
     }
     return si;
 }
@@ -68,7 +68,7 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
     const LightDev &light = rs.lights[lp.lidx];
     if (light.type != 0) return lp;  // infinite lights give nothing under allowIncompletePDF
     TriVerts lt = LoadTri(rs.prims, light.slot);
-    lp.ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, u0, u1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri).n);
+    lp.ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, u0, u1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri, lt.kind).n);
     V3 cp = Mid(ctx.pi);
     if (!lp.ss.ok || lp.ss.pdf == 0 || LengthSquared(Mid(lp.ss.pi) - cp) == 0) return lp;
     lp.wi = Normalize(Mid(lp.ss.pi) - cp);

@@ -135,8 +135,9 @@ class RenderScene:
             a = d["mesh_attr"][i]
             meshes[i] = capi.MeshAttr(int(a[0]), int(a[1]), int(max(a[2], 0)))
             if has_n[i]:
-                cn = np.ascontiguousarray(d["corner_n"][n_at:n_at + 3 * ntris[i]], np.float32)
-                n_at += 3 * int(ntris[i])
+                per = 4 if "mesh_kind" in d and d["mesh_kind"][i] == 1 else 3  # corners per primitive
+                cn = np.ascontiguousarray(d["corner_n"][n_at:n_at + per * ntris[i]], np.float32)
+                n_at += per * int(ntris[i])
                 meshes[i].corner_n = capi.fptr(cn)
                 keep.append(cn)
             if has_uv[i]:

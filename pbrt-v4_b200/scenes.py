@@ -440,14 +440,32 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
             pts = [(x0 + (x1 - x0) * u, height(u, v), z0 + (z1 - z0) * v) for v in g for u in g]
             idx = [k for j in range(n) for i in range(n)
                    for k in (j * (n + 1) + i, j * (n + 1) + i + 1, (j + 1) * (n + 1) + i, (j + 1) * (n + 1) + i + 1)]
-            return (f'Shape "bilinearmesh" "integer indices" [{" ".join(map(str, idx))}] "point3 P" '
-                    f'[{" ".join(f"{float(c):.7g}" for pt in pts for c in pt)}]')
+            txt = (f'Shape "bilinearmesh" "integer indices" [{" ".join(map(str, idx))}] "point3 P" '
+                   f'[{" ".join(f"{float(c):.7g}" for pt in pts for c in pt)}]')
+            if patches == "normals":  # vertex normals from the height field's finite differences (BilinearPatchMesh::n)
+                e = 1e-3
+                nrm = []
+                for v in g:
+                    for u in g:
+                        dx = (height(u + e, v) - height(u - e, v)) / (2 * e) / (x1 - x0)
+                        dz = (height(u, v + e) - height(u, v - e)) / (2 * e) / (z1 - z0)
+                        nv = np.array([-dx, 1.0, -dz])
+                        nrm.append(nv / np.linalg.norm(nv))
+                txt += f' "normal N" [{" ".join(f"{float(c):.7g}" for nv in nrm for c in nv)}]'
+            return txt
         lines += ['AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.25 0.35 0.75]',
                   '  ' + sheet(0.5, 0.92, 0.12, 0.55, 4, lambda u, v: 0.42 + 0.07 * np.sin(5.0 * u) * np.cos(4.0 * v) + 0.1 * u * v),
                   'AttributeEnd',
                   'AttributeBegin', '  ' + MATERIALS["conductor_rough"], '  ReverseOrientation',
                   '  ' + sheet(0.05, 0.3, 0.1, 0.45, 1, lambda u, v: 0.75 + 0.18 * (2 * u - 1) * (2 * v - 1)),
                   'AttributeEnd']
+        if patches == "normals":
+            # a twisted one-sided emitter whose vertex normals (towards the room) decide its emitting side
+            lines += ['AttributeBegin', '  AreaLightSource "diffuse" "rgb L" [3 6 9]',
+                      '  Material "diffuse" "rgb reflectance" [0 0 0]',
+                      '  Shape "bilinearmesh" "integer indices" [0 1 2 3] "point3 P" '
+                      '[0.3 0.55 0.93  0.5 0.5 0.97  0.32 0.8 0.97  0.52 0.75 0.9] '
+                      '"normal N" [0 0 -1  0.1 0 -1  0 0.1 -1  0.1 0.1 -1]', 'AttributeEnd']
     if alpha:
         # a 30 % screen in front of the camera and a fully cut-out (alpha 0) blocker under the light
         lines += ['AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.2 0.7 0.3]',

@@ -77,6 +77,8 @@ RENDER_CASES = {
     "cornell_smooth_r64_s16": dict(res=64, spp=16, maxdepth=5, smooth=True),
     # alpha cut-outs (constant alpha 0.5 / 0.3 / 0): the test runs inside traversal, for path and shadow rays alike
     "cornell_alpha_r64_s16": dict(res=64, spp=16, maxdepth=5, alpha=True),
+    # vertex normals on bilinear patches: shading geometry of a wavy sheet, an emitter oriented by its normals
+    "cornell_patchnormals_r64_s16": dict(res=64, spp=16, maxdepth=5, patches="normals"),
     "cornell_patchlights_r64_s16": dict(res=64, spp=16, maxdepth=5, patches="emissive", lightsampler="bvh"),
 }
 # Cases whose gate is the Monte-Carlo noise floor (rRMSE(ours, ref) <= 1.25 x rRMSE(ref seed s,
