@@ -778,7 +778,7 @@ def with_density_grid(d, density, medium=0):
 
 
 def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm", seed=0, grid=256, density=None,
-                 fog=True, crop=None, lightsampler="bvh"):
+                 fog=True, crop=None, lightsampler="bvh", patch_cap=False):
     """BASELINE configs[4]: VolPathIntegrator in the Cornell room: a thin homogeneous fog fills the room (an
     `interface` quad closes the open front; the camera stays in vacuum: a camera medium trips a race in the
     reference's BasicScene::GetMedium / CreateMedia, scene.cpp:809-850), and a box-shaped `interface` shell
@@ -805,7 +805,9 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
                   '"rgb sigma_s" [0.25 0.25 0.3] "float scale" 1 "float g" 0.3',
                   # front cap, normal towards the camera (-z): fog behind it, vacuum in front
                   'AttributeBegin', '  MediumInterface "fog" ""', '  Material "interface"',
-                  '  ' + _mesh_pbrt(_quad([0, 0, 0], [0, 1, 0], [1, 1, 0], [1, 0, 0])), 'AttributeEnd']
+                  # patch_cap: the same quad as ONE bilinear patch (medium transitions by a patch's normal)
+                  '  ' + ('Shape "bilinearmesh" "integer indices" [0 1 2 3] "point3 P" [0 0 0  0 1 0  1 0 0  1 1 0]'
+                          if patch_cap else _mesh_pbrt(_quad([0, 0, 0], [0, 1, 0], [1, 1, 0], [1, 0, 0]))), 'AttributeEnd']
     lo, hi = (0.22, 0.18, 0.25), (0.78, 0.74, 0.81)
     lines.append(f'MakeNamedMedium "cloud" "string type" "uniformgrid" "integer nx" {nx} "integer ny" {ny} "integer nz" {nz} '
                  f'"point3 p0" [{lo[0]} {lo[1]} {lo[2]}] "point3 p1" [{hi[0]} {hi[1]} {hi[2]}] '

@@ -161,6 +161,15 @@ def make_config5_goldens(P, refrun, out):
             img, secs = refrun.render(pbrt, pfm)
             np.save(os.path.join(out, "config5_small" + suffix), img.astype(np.float32))
         print("config5_small", img.shape, "mean", img.mean(axis=(0, 1)))
+        # the fog's front cap as a bilinear patch: medium transitions decided by a patch's normal
+        for seed, suffix in ((0, "_ref.npy"), (1, "_ref2.npy")):
+            P.scenes.config5_pbrt(pbrt, out=pfm, seed=seed, patch_cap=True, **CONFIG5_SMALL)
+            if seed == 0:
+                refrun.dump_scene(pbrt, os.path.join(out, "config5_patchcap_small.b2rs"))
+            img, secs = refrun.render(pbrt, pfm)
+            np.save(os.path.join(out, "config5_patchcap_small" + suffix), img.astype(np.float32))
+        if os.environ.get("B200PT_GOLDEN_PATCHCAP_ONLY"):
+            return
         # full-size frame, sampler and integrator tables around the small grid (bench.py swaps the 256^3 grid in)
         P.scenes.config5_pbrt(pbrt, out=pfm, **dict(CONFIG5_FULL, grid=CONFIG5_SMALL["grid"]))
         refrun.dump_scene(pbrt, os.path.join(out, "config5_full.b2rs"))

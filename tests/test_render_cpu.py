@@ -209,13 +209,14 @@ def test_realistic_camera_description_is_validated(P, rendercheck):
         rendercheck(P.RenderScene(d))
 
 
-def test_golden_image_config5_volpath(P, rendercheck):
-    """BASELINE configs[4] in miniature: VolPathIntegrator (cpu/integrators.cpp:953-1405) through a homogeneous
+@pytest.mark.parametrize("name", ["config5_small", "config5_patchcap_small"])
+def test_golden_image_config5_volpath(P, rendercheck, name):
+    """(config5_patchcap_small: the fog's front cap is a bilinear patch, so the medium transition goes by a patch's normal.)
+    BASELINE configs[4] in miniature: VolPathIntegrator (cpu/integrators.cpp:953-1405) through a homogeneous
     fog and a grid medium inside an interface shell: delta tracking over the majorant grid, real / null
     collisions with the r_u / r_l path probabilities, light samples whose transmittance walk crosses interfaces.
     The sampler dimensions and both RNG streams are the reference's, so paths follow the reference's; the gate is
     the noise floor, and the measured distance has to stay a small fraction of it."""
-    name = "config5_small"
     rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
     ref, ref2 = (np.load(os.path.join(GOLD, name + s)) for s in ("_ref.npy", "_ref2.npy"))
     assert int(rsc.d["integrator_type"][0]) == 1 and len(rsc.d["media_i"]) == 2
