@@ -500,8 +500,19 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
             if with_uv:
                 txt += f' "point2 uv" [{" ".join(f"{float(x):.7g}" for x in uv.reshape(-1))}]'
             return txt
-        lines += ['AttributeBegin', '  ' + MATERIALS["conductor_reflectance"], '  ' + ball((0.68, 0.5, 0.3), 0.16, 12, 8),
-                  'AttributeEnd',
+        if smooth == "instanced":
+            # the metal ball as an object instance under a rotation and a non-uniform scale: the interaction's
+            # shading normal and tangent go through Transform::operator()(SurfaceInteraction) (util/transform.cpp:227-258)
+            lines += ['AttributeBegin', '  ' + MATERIALS["conductor_reflectance"], '  ObjectBegin "ball"',
+                      '    ' + ball((0.0, 0.0, 0.0), 1.0, 12, 8), '  ObjectEnd', 'AttributeEnd',
+                      'AttributeBegin', '  Translate 0.68 0.5 0.3', '  Rotate 35 0.3 1 0.2', '  Scale 0.17 0.12 0.15',
+                      '  ObjectInstance "ball"', 'AttributeEnd',
+                      'AttributeBegin', '  Translate 0.3 0.25 0.2', '  Rotate -20 1 0 0.4', '  Scale 0.08 0.1 0.08',
+                      '  ObjectInstance "ball"', 'AttributeEnd']
+        else:
+            lines += ['AttributeBegin', '  ' + MATERIALS["conductor_reflectance"], '  ' + ball((0.68, 0.5, 0.3), 0.16, 12, 8),
+                      'AttributeEnd']
+        lines += [
                   'AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.3 0.6 0.7]',
                   '  ' + ball((0.25, 0.78, 0.35), 0.13, 10, 6, with_uv=False), 'AttributeEnd',
                   'AttributeBegin', '  AreaLightSource "diffuse" "rgb L" [4 5 9]',

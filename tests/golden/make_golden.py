@@ -75,6 +75,7 @@ RENDER_CASES = {
     # emissive patches: a rectangle (sampled as a spherical rectangle) and a twisted patch (by area), light BVH
     # per-vertex normals and uv on triangle meshes (shading geometry; an emissive dome oriented by its normals)
     "cornell_smooth_r64_s16": dict(res=64, spp=16, maxdepth=5, smooth=True),
+    "cornell_smoothinst_r64_s16": dict(res=64, spp=16, maxdepth=5, smooth="instanced"),
     # alpha cut-outs (constant alpha 0.5 / 0.3 / 0): the test runs inside traversal, for path and shadow rays alike
     "cornell_alpha_r64_s16": dict(res=64, spp=16, maxdepth=5, alpha=True),
     # vertex normals on bilinear patches: shading geometry of a wavy sheet, an emitter oriented by its normals
