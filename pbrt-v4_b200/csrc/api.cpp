@@ -111,6 +111,11 @@ int b200pt_context_destroy(b200pt_ctx *ctx) {
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->ownStream) cudaStreamDestroy(ctx->stream);
+    for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->evK) cudaEventDestroy(e);
+    if (ctx->evStart) cudaEventDestroy(ctx->evStart);
+    if (ctx->sIn) cudaStreamDestroy(ctx->sIn);
+    if (ctx->sOut) cudaStreamDestroy(ctx->sOut);
     delete ctx;
     return B200PT_OK;
 }
@@ -215,6 +220,52 @@ static int EnsureStaging(b200pt_ctx *ctx, size_t inBytes, size_t outBytes) {
     return B200PT_OK;
 }
 
+// Host-buffer batches (B200PT_MEM_HOST) go through in chunks on three streams: while chunk k is traversed, chunk k + 1
+// is on its way in and chunk k - 1 on its way out (PCIe is full duplex), so the call costs about the longest of the
+// three legs instead of their sum.  Chunks are independent ray ranges: results are those of one launch.
+static int IntersectHostPipelined(b200pt_scene *s, const float *rays, int64_t n, void *out, bool any) {
+    b200pt_ctx *ctx = s->ctx;
+    const size_t outRec = any ? 1 : sizeof(b200pt_hit);
+    int64_t chunk = 1 << 21;
+    if (const char *v = getenv("B200PT_HOST_CHUNK")) chunk = std::max<int64_t>(1 << 16, atoll(v));
+    const int64_t nChunks = (n + chunk - 1) / chunk;
+    if (!ctx->sIn) {
+        B2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sIn, cudaStreamNonBlocking));
+        B2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sOut, cudaStreamNonBlocking));
+        B2_CUDA(ctx, cudaEventCreateWithFlags(&ctx->evStart, cudaEventDisableTiming));
+    }
+    while (int64_t(ctx->evIn.size()) < nChunks) {
+        cudaEvent_t a, b;
+        B2_CUDA(ctx, cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        ctx->evIn.push_back(a);
+        B2_CUDA(ctx, cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        ctx->evK.push_back(b);
+    }
+    // whatever the caller queued on the context's stream before this call comes first
+    B2_CUDA(ctx, cudaEventRecord(ctx->evStart, ctx->stream));
+    B2_CUDA(ctx, cudaStreamWaitEvent(ctx->sIn, ctx->evStart, 0));
+    B2_CUDA(ctx, cudaStreamWaitEvent(ctx->sOut, ctx->evStart, 0));
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    for (int64_t k = 0; k < nChunks; ++k) {
+        const int64_t first = k * chunk, cnt = std::min(chunk, n - first);
+        const float *dR = (const float *)ctx->dIn + 7 * first;
+        char *dO = (char *)ctx->dOut + size_t(first) * outRec;
+        B2_CUDA(ctx, cudaMemcpyAsync((void *)dR, rays + 7 * first, size_t(cnt) * 28, cudaMemcpyHostToDevice, ctx->sIn));
+        B2_CUDA(ctx, cudaEventRecord(ctx->evIn[k], ctx->sIn));
+        B2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->evIn[k], 0));
+        B2_CUDA(ctx, LaunchTraversePersist(s->dev, dR, cnt, any ? nullptr : (b200pt_hit *)dO, any ? (unsigned char *)dO : nullptr, any,
+                                           (int *)(ctx->dCounters + 7), nullptr, ctx->smCount, int(s->dev.maxDepth) + 1,
+                                           ctx->refillMin, ctx->nodeMin, ctx->stream));
+        B2_CUDA(ctx, cudaEventRecord(ctx->evK[k], ctx->stream));
+        B2_CUDA(ctx, cudaStreamWaitEvent(ctx->sOut, ctx->evK[k], 0));
+        B2_CUDA(ctx, cudaMemcpyAsync((char *)out + size_t(first) * outRec, dO, size_t(cnt) * outRec, cudaMemcpyDeviceToHost, ctx->sOut));
+    }
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->sOut));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200PT_OK;
+}
+
 static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, uint32_t mem, bool any) {
     if (!s || n < 0 || (n > 0 && (!rays || !out))) return B200PT_ERR_INVALID;
     b200pt_ctx *ctx = s->ctx;
@@ -234,6 +285,7 @@ static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, u
     if (!device) {
         int rc = EnsureStaging(ctx, size_t(n) * 28, size_t(n) * outRec);
         if (rc != B200PT_OK) return rc;
+        if (!count && !ctx->simpleKernel && !getenv("B200PT_HOST_SERIAL")) return IntersectHostPipelined(s, rays, n, out, any);
         B2_CUDA(ctx, cudaMemcpyAsync(ctx->dIn, rays, size_t(n) * 28, cudaMemcpyHostToDevice, ctx->stream));
         dRays = (const float *)ctx->dIn;
         dOut = ctx->dOut;

@@ -1,6 +1,7 @@
 // api_internal.h - the handle structs behind include/b200pt.h, shared by api.cpp (geometry
 // entry points) and render_api.cpp (render entry points).
 #pragma once
+#include <vector>
 #include <cuda_runtime.h>
 
 #include <string>
@@ -10,6 +11,10 @@
 #include "scene_host.h"
 
 struct b200pt_ctx {
+    // host-buffer calls are pipelined in chunks: copy-in, traversal and copy-out of successive chunks overlap
+    cudaStream_t sIn = nullptr, sOut = nullptr;
+    std::vector<cudaEvent_t> evIn, evK;
+    cudaEvent_t evStart = nullptr;
     int device = 0;
     int smCount = 0;
     cudaStream_t stream = nullptr;
