@@ -142,6 +142,10 @@ typedef struct b200pt_trace_stats {
     uint64_t leaves_visited;
     uint64_t prims_tested;
     float kernel_ms; /* CUDA-event time of the traversal kernel(s) of the last call */
+    /* 8-wide nodes fetched (256 B each; nodes_visited counts their 8 box tests each) and rays that went through
+     * the exact binary kernel instead (non-finite 1/d or origin, at the top level or inside an instance) */
+    uint64_t wide_nodes_visited;
+    uint64_t exact_rays;
 } b200pt_trace_stats;
 
 enum { B200PT_TRACE_COUNTERS = 1u << 8 };

@@ -23,6 +23,24 @@ using namespace b200pt;
 
 std::string g_createErr;
 
+int EnsureExactScratch(b200pt_ctx *ctx, size_t n, int **out) {
+    *out = nullptr;
+    if (!ctx->wideKernel) return B200PT_OK;
+    if (n + 1 > ctx->dExactCap) {
+        if (ctx->dExact) {
+            B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            cudaFree(ctx->dExact);
+        }
+        ctx->dExact = nullptr;
+        ctx->dExactCap = 0;
+        B2_CUDA(ctx, cudaMalloc((void **)&ctx->dExact, (n + 1) * sizeof(int)));
+        ctx->dExactCap = n + 1;
+    }
+    *out = ctx->dExact;
+    return B200PT_OK;
+}
+
+
 extern "C" {
 
 int b200pt_version(void) { return B200PT_VERSION; }
@@ -77,6 +95,7 @@ int b200pt_context_create(int device, b200pt_ctx **out) {
     c->ownStream = true;
     const char *mode = getenv("B200PT_TRAVERSAL");
     c->simpleKernel = mode && std::string(mode) == "simple";
+    c->wideKernel = !(mode && (std::string(mode) == "binary" || std::string(mode) == "pair"));
     if (const char *v = getenv("B200PT_REFILL_MIN")) c->refillMin = std::max(1, std::min(32, atoi(v)));
     if (const char *v = getenv("B200PT_NODE_MIN")) c->nodeMin = std::max(1, std::min(32, atoi(v)));
     *out = c;
@@ -108,6 +127,7 @@ int b200pt_context_destroy(b200pt_ctx *ctx) {
     if (ctx->dIn) cudaFree(ctx->dIn);
     if (ctx->dOut) cudaFree(ctx->dOut);
     if (ctx->dCounters) cudaFree(ctx->dCounters);
+    if (ctx->dExact) cudaFree(ctx->dExact);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->ownStream) cudaStreamDestroy(ctx->stream);
@@ -145,6 +165,10 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
         e = cudaMemcpyAsync(s->dPairs, h.pairs.data(), h.pairs.size() * sizeof(PairNode), cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(s->dNodes, h.nodes.data(), nodeBytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(s->dPrims, h.prims.data(), primBytes, cudaMemcpyHostToDevice, ctx->stream);
+    size_t wideBytes = h.wide.size() * sizeof(Wide8);
+    if (e == cudaSuccess && wideBytes) e = cudaMalloc(&s->dWide, wideBytes);
+    if (e == cudaSuccess && wideBytes)
+        e = cudaMemcpyAsync(s->dWide, h.wide.data(), wideBytes, cudaMemcpyHostToDevice, ctx->stream);
     size_t instBytes = h.instances.size() * sizeof(InstanceDev);
     if (e == cudaSuccess && instBytes) e = cudaMalloc(&s->dInst, instBytes);
     if (e == cudaSuccess && instBytes)
@@ -160,6 +184,9 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     s->dev.pairs = s->dPairs;
     std::memcpy(s->dev.rootBox, h.bounds, 24);
     s->dev.rootRef = h.rootRef;
+    s->dev.wide = s->dWide;  // null when every tree is a single leaf: the binary kernel handles that
+    s->dev.rootWide = h.rootWide;
+    s->dev.maxStackWide = h.maxStackWide;
     s->dev.instances = (const InstanceDev *)s->dInst;
     s->dev.rootNode = h.rootNode;
     s->dev.nNodes = uint32_t(h.nodes.size());
@@ -170,8 +197,8 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     s->stats.n_triangles = h.nTriangles;
     s->stats.n_instances = h.instances.size();
     s->stats.n_bvh2_nodes = h.nodes.size();
-    s->stats.n_wide_nodes = h.pairs.size();
-    s->stats.device_bytes = nodeBytes + primBytes + pairBytes + instBytes;
+    s->stats.n_wide_nodes = h.wide.size();
+    s->stats.device_bytes = nodeBytes + primBytes + pairBytes + instBytes + wideBytes;
     s->stats.build_seconds = h.buildSeconds;
     s->stats.upload_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     *out = s;
@@ -185,6 +212,7 @@ int b200pt_scene_destroy(b200pt_scene *s) {
     if (s->dNodes) cudaFree(s->dNodes);
     if (s->dPrims) cudaFree(s->dPrims);
     if (s->dPairs) cudaFree(s->dPairs);
+    if (s->dWide) cudaFree(s->dWide);
     if (s->dInst) cudaFree(s->dInst);
     delete s;
     return B200PT_OK;
@@ -229,6 +257,8 @@ static int IntersectHostPipelined(b200pt_scene *s, const float *rays, int64_t n,
     int64_t chunk = 1 << 21;
     if (const char *v = getenv("B200PT_HOST_CHUNK")) chunk = std::max<int64_t>(1 << 16, atoll(v));
     const int64_t nChunks = (n + chunk - 1) / chunk;
+    int *exact = nullptr;
+    if (int rc = EnsureExactScratch(ctx, size_t(std::min(chunk, n)), &exact)) return rc;
     if (!ctx->sIn) {
         B2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sIn, cudaStreamNonBlocking));
         B2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->sOut, cudaStreamNonBlocking));
@@ -255,7 +285,7 @@ static int IntersectHostPipelined(b200pt_scene *s, const float *rays, int64_t n,
         B2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->evIn[k], 0));
         B2_CUDA(ctx, LaunchTraversePersist(s->dev, dR, cnt, any ? nullptr : (b200pt_hit *)dO, any ? (unsigned char *)dO : nullptr, any,
                                            (int *)(ctx->dCounters + 7), nullptr, ctx->smCount, int(s->dev.maxDepth) + 1,
-                                           ctx->refillMin, ctx->nodeMin, ctx->stream));
+                                           ctx->refillMin, ctx->nodeMin, ctx->stream, false, nullptr, exact));
         B2_CUDA(ctx, cudaEventRecord(ctx->evK[k], ctx->stream));
         B2_CUDA(ctx, cudaStreamWaitEvent(ctx->sOut, ctx->evK[k], 0));
         B2_CUDA(ctx, cudaMemcpyAsync((char *)out + size_t(first) * outRec, dO, size_t(cnt) * outRec, cudaMemcpyDeviceToHost, ctx->sOut));
@@ -296,6 +326,9 @@ static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, u
         ctx->err = "B200PT_TRAVERSAL=simple (the parity kernel) does not handle object instances";
         return B200PT_ERR_INVALID;
     }
+    int *exact = nullptr;
+    if (!ctx->simpleKernel)
+        if (int rc = EnsureExactScratch(ctx, size_t(n), &exact)) return rc;
     if (ctx->simpleKernel)
         B2_CUDA(ctx, LaunchTraverseBVH2(s->dev, dRays, n, any ? nullptr : (b200pt_hit *)dOut,
                                         any ? (unsigned char *)dOut : nullptr, any,
@@ -305,7 +338,7 @@ static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, u
                                            any ? (unsigned char *)dOut : nullptr, any,
                                            (int *)(ctx->dCounters + 7), count ? ctx->dCounters : nullptr,
                                            ctx->smCount, int(s->dev.maxDepth) + 1, ctx->refillMin, ctx->nodeMin,
-                                           ctx->stream));
+                                           ctx->stream, false, nullptr, exact));
     B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     if (!device) {
         B2_CUDA(ctx, cudaMemcpyAsync(out, dOut, size_t(n) * outRec, cudaMemcpyDeviceToHost, ctx->stream));
@@ -318,6 +351,13 @@ static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, u
         s->trace.nodes_visited = c[0];
         s->trace.leaves_visited = c[1];
         s->trace.prims_tested = c[2];
+        s->trace.wide_nodes_visited = c[3];
+        if (exact) {
+            int nExact = 0;
+            B2_CUDA(ctx, cudaMemcpyAsync(&nExact, exact, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            s->trace.exact_rays = uint64_t(nExact);
+        }
     }
     return B200PT_OK;
 }

@@ -30,13 +30,20 @@ struct b200pt_ctx {
     // scheduling knobs of the persistent kernel (B200PT_REFILL_MIN / B200PT_NODE_MIN override)
     int refillMin = 4, nodeMin = 16;
     bool simpleKernel = false;  // B200PT_TRAVERSAL=simple: the one-thread-per-ray parity kernel
+    bool wideKernel = true;     // B200PT_TRAVERSAL=binary: the exact binary kernel for every ray
+    // [0] = count, [1..] = indices of the rays the wide kernel handed to the exact binary kernel (grow-only)
+    int *dExact = nullptr;
+    size_t dExactCap = 0;
 };
+
+// device scratch for `n` rays of a wide-kernel launch, or null when the wide kernel is off; B200PT_ERR_* on failure
+int EnsureExactScratch(b200pt_ctx *ctx, size_t n, int **out);
 
 struct b200pt_scene {
     b200pt_ctx *ctx = nullptr;
     b200pt::HostScene host;
     b200pt::DeviceScene dev{};
-    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr, *dPairs = nullptr;
+    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr, *dPairs = nullptr, *dWide = nullptr;
     b200pt_scene_stats stats{};
     b200pt_trace_stats trace{};
 };

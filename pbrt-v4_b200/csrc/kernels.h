@@ -15,6 +15,6 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
                                   unsigned char *occluded, bool any, int *rayCounter,
                                   unsigned long long *counters, int smCount, int stackDepth,
                                   int refillMin, int nodeMin, cudaStream_t stream, bool internalHits = false,
-                                  const int *nDev = nullptr);
+                                  const int *nDev = nullptr, int *exactScratch = nullptr);
 
 }  // namespace b200pt

@@ -200,6 +200,8 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
         r->pathCap = need;
     }
     const PassBuffers &pb = r->pb;
+    int *exact = nullptr;
+    if (int rc = EnsureExactScratch(ctx, size_t(need), &exact)) return rc;
     int launches = 0;
     B2_CUDA(ctx, cudaMemsetAsync(r->dCounters, 0, 4 * sizeof(unsigned long long), ctx->stream));
     B2_CUDA(ctx, cudaEventRecord(r->ev0, ctx->stream));
@@ -219,7 +221,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                 const int *nRays = pb.counts + kCountStride * j, *nShadow = nRays + 1;
                 B2_CUDA(ctx, LaunchTraversePersist(sc, pb.rays[j & 1], nActive, (b200pt_hit *)pb.hits, nullptr, false,
                                                    r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
-                                                   ctx->nodeMin, ctx->stream, true, nRays));
+                                                   ctx->nodeMin, ctx->stream, true, nRays, exact));
                 ++launches;
                 if (r->dev.nMedia) {
                     B2_CUDA(ctx, LaunchVolMedium(r->dev, pb, j, nPix, width, nActive, ctx->stream, r->volWarp));
@@ -239,7 +241,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                     B2_CUDA(ctx, cudaMemsetAsync(pb.shContinue, 0, sizeof(int), ctx->stream));
                     B2_CUDA(ctx, LaunchTraversePersist(sc, pb.shRays, hc[0], (b200pt_hit *)pb.shHits, nullptr, false,
                                                        r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
-                                                       ctx->nodeMin, ctx->stream, true, nShadow));
+                                                       ctx->nodeMin, ctx->stream, true, nShadow, exact));
                     B2_CUDA(ctx, LaunchShadowTr(r->dev, pb, j, hc[0], ctx->stream, r->volWarp));
                     launches += 5;
                     B2_CUDA(ctx, cudaMemcpyAsync(&live, pb.shContinue, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
@@ -264,14 +266,14 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
             const int *nRays = pb.counts + kCountStride * j, *nShadow = nRays + 1;
             B2_CUDA(ctx, LaunchTraversePersist(sc, pb.rays[j & 1], nActive, (b200pt_hit *)pb.hits, nullptr, false,
                                                r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
-                                               ctx->nodeMin, ctx->stream, true, nRays));
+                                               ctx->nodeMin, ctx->stream, true, nRays, exact));
             B2_CUDA(ctx, LaunchClassify(r->dev, pb, j, nActive, ctx->stream));
             launches += 2;
             B2_CUDA(ctx, LaunchShade(r->dev, pb, j, nPix, width, nActive, r->matMask, ctx->stream, &launches));
             if (j < maxDepth) {
                 B2_CUDA(ctx, LaunchTraversePersist(sc, pb.shRays, nActive, nullptr, pb.occluded, true, r->dRayCounter,
                                                    nullptr, ctx->smCount, stackDepth, ctx->refillMin, ctx->nodeMin,
-                                                   ctx->stream, false, nShadow));
+                                                   ctx->stream, false, nShadow, exact));
                 B2_CUDA(ctx, LaunchResolveShadows(pb, j, nActive, ctx->stream));
                 launches += 2;
             }

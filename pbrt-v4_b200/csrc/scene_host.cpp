@@ -349,6 +349,21 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             out.treeRootRef.push_back(refOf[r]);
         out.rootRef = out.treeRootRef[0];
     }
+    // ---- the 8-wide collapse of every tree
+    out.wide.clear();
+    out.treeRootWide.clear();
+    {
+        uint32_t topStack = 1, objStack = 0;
+        for (size_t ti = 0; ti < out.trees.size(); ++ti) {
+            uint32_t st = 1;
+            out.treeRootWide.push_back(BuildWide(out.nodes, out.treeRoot[ti], out.wide, &st));
+            if (ti == 0) topStack = st;
+            else objStack = std::max(objStack, st);
+        }
+        out.rootWide = out.treeRootWide[0];
+        // an instance is entered from a top-level leaf: two entries hold the way back (traverse_wide.cu)
+        out.maxStackWide = topStack + (objStack ? objStack + 2 : 0);
+    }
     // ---- instance table
     out.instances.clear();
     {
@@ -370,6 +385,7 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
             std::memcpy(d.rootBox + 3, root.bmax, 12);
             d.rootRef = out.treeRootRef[it->second];
             d.rootNode = out.treeRoot[it->second];
+            d.rootWide = out.treeRootWide[it->second];
             d.instanceId = i + 1;
             d.object = in.object;
             out.instances.push_back(d);

@@ -10,6 +10,7 @@
 #include "../../include/b200pt.h"
 #include "bvh2.h"
 #include "device_scene.h"
+#include "wide.h"
 
 namespace b200pt {
 
@@ -26,6 +27,10 @@ struct HostScene {
     std::vector<PairNode> pairs;     // production layout (interior nodes only)
     std::vector<int32_t> treeRootRef; // per tree: PairNode index or ~slot
     int32_t rootRef = 0;
+    std::vector<Wide8> wide;         // 8-wide collapse of the same trees (traverse_wide.cu)
+    std::vector<int32_t> treeRootWide; // per tree: Wide8 index or ~slot
+    int32_t rootWide = 0;
+    uint32_t maxStackWide = 1;       // stack entries the wide traversal can need (top level + deepest object)
     std::vector<InstanceDev> instances;
     std::vector<uint32_t> treeRoot;  // root node of trees[i] in `nodes`
     uint32_t rootNode = 0;

@@ -1,4 +1,5 @@
-// traverse_persist.cu - the production closest-hit / any-hit kernels over the binary tree.
+// traverse_persist.cu - the production closest-hit / any-hit kernels: the 8-wide walk (WIDE, wide.h) and the
+// exact binary walk it hands irregular rays to.
 //
 // Same visit order as BVHAggregate::Intersect / IntersectP (reference
 // cpu/aggregates.cpp:529-624) - near child first by dirIsNeg[axis], far child
@@ -19,6 +20,7 @@
 #include "instance.h"
 #include "isect.h"
 #include "kernels.h"
+#include "wide.h"
 #include "../../include/b200pt.h"
 
 namespace b200pt {
@@ -51,7 +53,7 @@ enum : int { S_IDLE = 0, S_NODE = 1, S_LEAF = 2, S_DONE = 3 };
 // util/vecmath.h:1609) is re-evaluated when the entry is popped - i.e. at the moment the
 // reference would have tested that node.
 constexpr int kSmemDepth = 24;
-constexpr int kLocalDepth = 72;
+constexpr int kLocalDepth = 104;
 
 // INTERNAL: closest-hit records for the shading kernels {slot, t, b0, b1, b2, instance + 1} instead of
 // the public b200pt_hit (the PrimSlot index saves the shader the (mesh, tri) -> vertices lookup).
@@ -63,17 +65,22 @@ constexpr int kLocalDepth = 72;
 // goes on with tMax = the t found in the object, not shifted back by dt, as the reference does.
 constexpr int kReturn = int(0x80000000u);
 // PATCH: some leaf slots are bilinear patches (kind word of the slot's last 16 bytes); hits report (u, v).
-template <bool ANY, bool COUNT, bool INTERNAL, bool INST, bool PATCH>
+// WIDE: interior nodes are Wide8 (wide.h): eight exact child boxes per visit, children stacked in the reference's
+// visit order by pre-set popcount.  A ray whose 1/d or origin is not finite - at fetch, or as transformed into an
+// instance - is appended to `exactList` and dropped; the launcher runs the binary variant over that list afterwards
+// (`indexList` = the list, `nDev` = its length).
+template <bool ANY, bool COUNT, bool INTERNAL, bool INST, bool PATCH, bool WIDE>
 __global__ void __launch_bounds__(kBlock)
 TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200pt_hit *__restrict__ hits,
                       unsigned char *__restrict__ occluded, int *__restrict__ rayCounter,
                       unsigned long long *__restrict__ counters, int kRefillMin, int kNodeMin,
-                      const int *__restrict__ nDev) {
+                      const int *__restrict__ nDev, const int *__restrict__ indexList, int *__restrict__ exactList,
+                      int *__restrict__ exactCount) {
     if (nDev) n = min(n, *nDev);  // queue length written by an earlier kernel of the stream
     __shared__ int2 smemStack[kSmemDepth * kBlock];
     int2 *stack = smemStack + threadIdx.x;  // entry d lives at stack[d * kBlock]
     int2 deep[kLocalDepth];
-    const char *pairs = reinterpret_cast<const char *>(sc.pairs);
+    const char *pairs = reinterpret_cast<const char *>(WIDE ? sc.wide : sc.pairs);
     const char *prims = reinterpret_cast<const char *>(sc.prims);
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -86,7 +93,23 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
     int lslot = 0, lrem = 0;                 // leaf cursor: next slot, slots left (0 = read the leaf header)
     int curInst = -1, bestInst = -1;         // instance being traversed / instance of the best hit
     bool instHit = false;                    // a hit was accepted inside the current instance
-    unsigned long long cNodes = 0, cLeaves = 0, cPrims = 0;
+    unsigned long long cNodes = 0, cLeaves = 0, cPrims = 0, cWide = 0;
+    bool flip = false;  // WIDE: dirIsNeg[2] - the stored visit orders are those of dirIsNeg[2] == 0, reversed otherwise
+    int cls = 0;        // WIDE: dirIsNeg[0] | dirIsNeg[1] << 1 of the octant whose order is stored
+    auto regular = [&]() {
+        // a NaN or an infinity anywhere makes the sum of magnitudes non-finite (so does an overflow of finite
+        // terms: that ray merely takes the exact kernel too)
+        return ((fabsf(r.ix) + fabsf(r.iy)) + (fabsf(r.iz) + fabsf(r.ox)) + (fabsf(r.oy) + fabsf(r.oz))) < INFINITY;
+    };
+    auto setOctant = [&]() {
+        flip = r.neg[2] != 0;
+        cls = (r.neg[0] ^ int(flip)) | ((r.neg[1] ^ int(flip)) << 1);
+    };
+    // hands the ray over to the exact binary kernel
+    auto giveUp = [&]() {
+        exactList[atomicAdd(exactCount, 1)] = rayIdx;
+        state = S_IDLE;
+    };
 
     auto push = [&](int ref, int tbits) {
         int2 e = make_int2(ref, tbits);
@@ -117,6 +140,7 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                 int2 saved = pop();
                 const float *q = rays + 7ll * rayIdx;
                 RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
+                if (WIDE) setOctant();
                 if (!instHit) tMax = __int_as_float(saved.y);
                 curInst = -1;
                 if (saved.x > 0) {
@@ -147,6 +171,7 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                 if (state == S_IDLE) {
                     int my = base + __popc(idle & ((1u << lane) - 1));
                     if (my < n) {
+                        if (indexList) my = indexList[my];
                         const float *q = rays + 7ll * my;
                         RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
                         tMax = q[6];
@@ -157,7 +182,9 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                         bestInst = -1;
                         // the reference tests the root's own box first (cpu/aggregates.cpp:545)
                         if (COUNT) ++cNodes;
-                        if (SlabTest(r, sc.rootBox, sc.rootBox + 3, tMax)) enter(sc.rootRef);
+                        if (WIDE) setOctant();
+                        if (WIDE && !regular()) giveUp();
+                        else if (SlabTest(r, sc.rootBox, sc.rootBox + 3, tMax)) enter(WIDE ? sc.rootWide : sc.rootRef);
                         else state = S_DONE;
                     }
                 }
@@ -171,6 +198,62 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
         unsigned inNode;
         do {
             if (state == S_NODE) {
+                if (WIDE) {
+                    const char *np = pairs + 256ll * cur;
+                    if (COUNT) {
+                        cNodes += 8;
+                        ++cWide;
+                    }
+                    // children are stacked when the tMax-independent part of the reference's test passes and their
+                    // entry distance is below tMax with a margin (tMax can still creep up by rounding, wide.h);
+                    // `tMin < tMax` itself is decided when the entry is popped
+                    const float tMaxS = __fmaf_rn(fabsf(tMax), 0x1p-10f, tMax);
+                    unsigned H = 0;
+                    float tm[8];
+                    Node8f a0 = Load256(np), b0 = Load256(np + 32), c0 = Load256(np + 64);
+                    Node8f a1 = Load256(np + 96), b1 = Load256(np + 128), c1 = Load256(np + 160);
+                    {
+                        const float bx[24] = {a0.v[0], a0.v[1], a0.v[2], a0.v[3], a0.v[4], a0.v[5], a0.v[6], a0.v[7],
+                                              b0.v[0], b0.v[1], b0.v[2], b0.v[3], b0.v[4], b0.v[5], b0.v[6], b0.v[7],
+                                              c0.v[0], c0.v[1], c0.v[2], c0.v[3], c0.v[4], c0.v[5], c0.v[6], c0.v[7]};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            bool ok = SlabCore(r, bx + 6 * j, bx + 6 * j + 3, tm[j]) & (tm[j] < tMaxS);
+                            H |= unsigned(ok) << j;
+                        }
+                    }
+                    {
+                        const float bx[24] = {a1.v[0], a1.v[1], a1.v[2], a1.v[3], a1.v[4], a1.v[5], a1.v[6], a1.v[7],
+                                              b1.v[0], b1.v[1], b1.v[2], b1.v[3], b1.v[4], b1.v[5], b1.v[6], b1.v[7],
+                                              c1.v[0], c1.v[1], c1.v[2], c1.v[3], c1.v[4], c1.v[5], c1.v[6], c1.v[7]};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            bool ok = SlabCore(r, bx + 6 * j, bx + 6 * j + 3, tm[4 + j]) & (tm[4 + j] < tMaxS);
+                            H |= unsigned(ok) << (4 + j);
+                        }
+                    }
+                    if (H) {
+                        Node8f rf = Load256(np + 192);
+                        const uint2 pre = __ldg(reinterpret_cast<const uint2 *>(np + 224) + cls);
+                        const int nHit = __popc(H);
+                        // rank in the reference's visit order = hits among the slots visited before this one; the
+                        // first to be visited ends on top of the stack (reversed order when dirIsNeg[2])
+                        const int base = flip ? sp : sp + nHit - 1;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            if ((H >> i) & 1u) {
+                                const unsigned before = ((i < 4 ? pre.x : pre.y) >> (8 * (i & 3))) & 0xffu;
+                                const int rk = __popc(H & before);
+                                const int idx = flip ? base + rk : base - rk;
+                                const int2 e = make_int2(__float_as_int(rf.v[i]), __float_as_int(tm[i]));
+                                if (idx < kSmemDepth) stack[idx * kBlock] = e;
+                                else deep[idx - kSmemDepth] = e;
+                            }
+                        }
+                        sp += nHit;
+                    }
+                    popNext();
+                } else {
                 if (COUNT) cNodes += 2;
                 Node8f a = Load256(pairs + 64ll * cur), b = Load256(pairs + 64ll * cur + 32);
                 float t0, t1;
@@ -188,6 +271,7 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                 if (hFar) push(farRef, __float_as_int(tFar));
                 if (hNear) enter(nearRef);
                 else popNext();
+                }
             }
             inNode = __ballot_sync(FULL, state == S_NODE);
         } while (__popc(inNode) >= kNodeMin);
@@ -215,7 +299,15 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                     tMax = tMax2;
                     curInst = __float_as_int(b.z);
                     instHit = false;
-                    int rootRef = __ldg(&in->rootRef);
+                    if (WIDE) {
+                        setOctant();
+                        if (!regular()) {  // the transformed ray breaks the wide walk's premise: redo the whole ray exactly
+                            giveUp();
+                            entered = true;
+                            break;
+                        }
+                    }
+                    int rootRef = __ldg(WIDE ? &in->rootWide : &in->rootRef);
                     bool go = true;
                     if (rootRef >= 0) {  // a one-primitive object has no BVH and no box test
                         float box[6];
@@ -309,19 +401,23 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
         atomicAdd(counters + 0, cNodes);
         atomicAdd(counters + 1, cLeaves);
         atomicAdd(counters + 2, cPrims);
+        atomicAdd(counters + 3, cWide);
     }
 }
 
+// exactScratch: 1 + n ints of device memory ([0] = length of the list that follows) for the rays the wide kernel
+// hands to the exact binary kernel; null = binary kernel only.
 cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long long n, b200pt_hit *hits,
                                   unsigned char *occluded, bool any, int *rayCounter,
                                   unsigned long long *counters, int smCount, int stackDepth,
                                   int refillMin, int nodeMin, cudaStream_t stream, bool internalHits,
-                                  const int *nDev) {
+                                  const int *nDev, int *exactScratch) {
     if (n <= 0) return cudaSuccess;
     if (n > 0x7fffffffll) return cudaErrorInvalidValue;
     if (stackDepth > kSmemDepth + kLocalDepth) return cudaErrorInvalidValue;
+    const bool wide = exactScratch && sc.wide && int(sc.maxStackWide) + 2 <= kSmemDepth + kLocalDepth;
     size_t smemBytes = 0;
-    auto pick = [&](auto kern) -> cudaError_t {
+    auto pick = [&](auto kern, bool wideLaunch, const int *nDevK, const int *indexList) -> cudaError_t {
         int perSM = 0;
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, kBlock, smemBytes);
         if (e != cudaSuccess) return e;
@@ -331,19 +427,33 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
         int grid = (int)(want < cap ? want : cap);
         e = cudaMemsetAsync(rayCounter, 0, sizeof(int), stream);
         if (e != cudaSuccess) return e;
+        if (wideLaunch) {
+            e = cudaMemsetAsync(exactScratch, 0, sizeof(int), stream);
+            if (e != cudaSuccess) return e;
+        }
         kern<<<grid, kBlock, smemBytes, stream>>>(sc, rays, (int)n, hits, occluded, rayCounter, counters, refillMin,
-                                                  nodeMin, nDev);
+                                                  nodeMin, nDevK, indexList, wideLaunch ? exactScratch + 1 : nullptr,
+                                                  wideLaunch ? exactScratch : nullptr);
         return cudaGetLastError();
     };
-#define B2_PICK(ANYV, INTV, INSTV, PATCHV)                                                        \
-    (counters ? pick(TraversePersistKernel<ANYV, true, INTV, INSTV, PATCHV>)                      \
-              : pick(TraversePersistKernel<ANYV, false, INTV, INSTV, PATCHV>))
-#define B2_PICK_SCENE(ANYV, INTV)                                                                 \
-    (sc.nInstances ? (sc.hasPatches ? B2_PICK(ANYV, INTV, true, true) : B2_PICK(ANYV, INTV, true, false)) \
-                   : (sc.hasPatches ? B2_PICK(ANYV, INTV, false, true) : B2_PICK(ANYV, INTV, false, false)))
-    if (any) return B2_PICK_SCENE(true, false);
-    if (internalHits) return B2_PICK_SCENE(false, true);
-    return B2_PICK_SCENE(false, false);
+#define B2_PICK(ANYV, INTV, INSTV, PATCHV, WIDEV, ...)                                            \
+    (counters ? pick(TraversePersistKernel<ANYV, true, INTV, INSTV, PATCHV, WIDEV>, __VA_ARGS__)  \
+              : pick(TraversePersistKernel<ANYV, false, INTV, INSTV, PATCHV, WIDEV>, __VA_ARGS__))
+#define B2_PICK_SCENE(ANYV, INTV, WIDEV, ...)                                                     \
+    (sc.nInstances ? (sc.hasPatches ? B2_PICK(ANYV, INTV, true, true, WIDEV, __VA_ARGS__)         \
+                                    : B2_PICK(ANYV, INTV, true, false, WIDEV, __VA_ARGS__))       \
+                   : (sc.hasPatches ? B2_PICK(ANYV, INTV, false, true, WIDEV, __VA_ARGS__)        \
+                                    : B2_PICK(ANYV, INTV, false, false, WIDEV, __VA_ARGS__)))
+#define B2_PICK_KIND(WIDEV, ...)                                                                  \
+    (any ? B2_PICK_SCENE(true, false, WIDEV, __VA_ARGS__)                                         \
+         : (internalHits ? B2_PICK_SCENE(false, true, WIDEV, __VA_ARGS__)                         \
+                         : B2_PICK_SCENE(false, false, WIDEV, __VA_ARGS__)))
+    if (!wide) return B2_PICK_KIND(false, false, nDev, nullptr);
+    cudaError_t e = B2_PICK_KIND(true, true, nDev, nullptr);
+    if (e != cudaSuccess) return e;
+    // the rays the wide walk declined (non-finite 1/d or origin), if any: exact binary walk over the list
+    return B2_PICK_KIND(false, false, exactScratch, exactScratch + 1);
+#undef B2_PICK_KIND
 #undef B2_PICK_SCENE
 #undef B2_PICK
 }

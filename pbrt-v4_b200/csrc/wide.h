@@ -1,0 +1,48 @@
+// wide.h - the 8-wide node of the production traversal kernel (traverse_wide.cu).
+//
+// A wide node stands for one interior node R of the reference's binary tree (LinearBVHNode,
+// cpu/aggregates.cpp:129-137) and holds a CUT of R's subtree: up to eight descendants, each a binary
+// leaf or a binary interior node (which then has a wide node of its own), with THE REFERENCE'S OWN fp32
+// box of that descendant, bit for bit.  The binary nodes between R and the cut are not tested.
+//
+// Why the hits stay bit-identical to BVHAggregate::Intersect (cpu/aggregates.cpp:529-579):
+//   (1) Bounds3::IntersectP (util/vecmath.h:1576-1610) is monotone in the box for a ray whose 1/d is
+//       finite: a box inside another one has tMin >= and tMax <= the outer one's, float for float
+//       (subtraction and multiplication by a fixed factor are monotone), so "a leaf passes its own
+//       test with the tMax of its turn" implies "every ancestor passed at its turn" - between an
+//       ancestor's turn and the first leaf under it no primitive is tested, and if the ancestor fails
+//       nothing under it can pass either.  Hence: the reference visits exactly the leaves that pass
+//       their own test at their turn, and it is enough to (a) take the leaves in the reference's order
+//       and (b) apply the exact test to each leaf's box with the tMax of that moment.
+//   (2) The order: near child first by dirIsNeg[axis] at every binary node (cpu/aggregates.cpp:562-568).
+//       Inside a wide node that is a permutation of the slots per ray octant; `pre` stores, for the four
+//       octants with dirIsNeg[2] == 0, the set of slots visited before each slot (the other four octants
+//       visit in exactly the reversed order).
+//   (3) tMax is not monotone (an accepted t may round above the tMax it was tested against,
+//       shapes.cpp:239-250), so children are stacked on the tMax-independent part of the test plus
+//       `tMin < tMax * (1 + 2^-10)`, and `tMin < tMax` is decided when the entry is popped.
+//   Rays with a non-finite 1/d or origin (0 * inf = NaN breaks (1)) take the exact binary kernel
+//   (traverse_persist.cu) instead; the wide kernel hands them over through a device-side list.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+#include "bvh2.h"
+
+namespace b200pt {
+
+struct alignas(128) Wide8 {
+    float box[8][6];    // child i: pMin xyz, pMax xyz (empty slot: +inf / -inf, never passes)
+    int32_t ref[8];     // >= 0: Wide8 index; < 0: leaf, first PrimSlot = ~ref (count in that slot's `flags`)
+    uint8_t pre[4][8];  // [negx | negy << 1][slot] = bit mask of the slots visited before `slot` (negz = 0)
+};
+static_assert(sizeof(Wide8) == 256, "Wide8 is eight 32-byte loads");
+constexpr int32_t kWideEmpty = int32_t(0x7fffffff);
+
+// Collapses one binary tree (nodes[root..], absolute child offsets, leaves' `offset` = first PrimSlot)
+// into wide nodes appended to `out`.  Returns the tree's root reference: a Wide8 index, or ~slot when the
+// root is a leaf.  `maxStackOut` = the most traversal-stack entries a ray can hold inside this tree
+// (every visited node stacks all its children and pops one).
+int32_t BuildWide(const std::vector<Node32> &nodes, uint32_t root, std::vector<Wide8> &out, uint32_t *maxStackOut);
+
+}  // namespace b200pt

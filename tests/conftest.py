@@ -36,8 +36,9 @@ def hostcheck_bin():
     out = os.path.join(ROOT, "tests", "native", "_build", "hostcheck")
     src = [os.path.join(ROOT, "tests", "native", "hostcheck.cpp"),
            os.path.join(ROOT, "pbrt-v4_b200", "csrc", "scene_host.cpp"),
-           os.path.join(ROOT, "pbrt-v4_b200", "csrc", "bvh2_build.cpp")]
-    deps = src + [os.path.join(ROOT, "pbrt-v4_b200", "csrc", h) for h in ("isect.h", "instance.h", "scene_host.h", "bvh2.h")] \
+           os.path.join(ROOT, "pbrt-v4_b200", "csrc", "bvh2_build.cpp"),
+           os.path.join(ROOT, "pbrt-v4_b200", "csrc", "wide_build.cpp")]
+    deps = src + [os.path.join(ROOT, "pbrt-v4_b200", "csrc", h) for h in ("isect.h", "instance.h", "scene_host.h", "bvh2.h", "wide.h")] \
         + [os.path.join(ROOT, "tests", "native", "trace_host.h")]
     if not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in deps):
         os.makedirs(os.path.dirname(out), exist_ok=True)
@@ -78,7 +79,7 @@ def rendercheck(P):
     csrc = os.path.join(ROOT, "pbrt-v4_b200", "csrc")
     out = os.path.join(ROOT, "tests", "native", "_build", "librendercheck.so")
     src = [os.path.join(ROOT, "tests", "native", "rendercheck.cpp")] + \
-          [os.path.join(csrc, f) for f in ("scene_host.cpp", "bvh2_build.cpp", "render_host.cpp")]
+          [os.path.join(csrc, f) for f in ("scene_host.cpp", "bvh2_build.cpp", "wide_build.cpp", "render_host.cpp")]
     deps = src + [os.path.join(csrc, h) for h in os.listdir(csrc) if h.endswith(".h")] \
         + [os.path.join(ROOT, "tests", "native", "trace_host.h")]
     if not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in deps):

@@ -4,7 +4,7 @@
 // compared bit-for-bit with the compiled reference in the GPU-less container.
 // It is not part of libb200pt.so and nothing in the product calls it.
 //   hostcheck scene.b2sc rays.f32 {closest|any|closest2|any2} out.bin
-// closest2/any2 walk the production PairNode layout with the {ref, tMin} stack and the pop-time
+// closest8/any8 walk the Wide8 layout as traverse_wide.cu does; closest2/any2 walk the PairNode layout with the {ref, tMin} stack and the pop-time
 // `tMin < tMax` re-check exactly as traverse_persist.cu does.
 #include <cstdio>
 #include <cstdlib>
@@ -115,8 +115,10 @@ int main(int argc, char **argv) {
     if (fread(rays.data(), 4, rays.size(), rf) != rays.size()) return 2;
     fclose(rf);
     std::string mode = argv[3];
-    bool any = mode == "any" || mode == "any2";
+    bool any = mode == "any" || mode == "any2" || mode == "any8";
     bool pairMode = mode == "closest2" || mode == "any2";
+    bool wideMode = mode == "closest8" || mode == "any8";
+    size_t nIrregular = 0;
     std::vector<b200pt_hit> hits(any ? 0 : n);
     std::vector<uint8_t> occ(any ? n : 0);
     for (size_t i = 0; i < n; ++i) {
@@ -124,7 +126,19 @@ int main(int argc, char **argv) {
         float tMax = q[6];
         bool dbg = getenv("RAYDBG") && (size_t)atol(getenv("RAYDBG")) == i;
         Best best;
-        bool h = pairMode ? TracePairs(hs, hs.rootRef, hs.bounds, q, q + 3, tMax, any, best, -1, dbg)
+        bool h = false;
+        int hw = -1;
+        if (wideMode) {
+            hw = TraceWide(hs, hs.rootWide, hs.bounds, q, q + 3, tMax, any, best, -1);
+            if (hw < 0) {  // irregular ray: the exact binary walk, from scratch
+                ++nIrregular;
+                tMax = q[6];
+                best = Best();
+            }
+            h = hw > 0;
+        }
+        if (hw < 0)
+            h = (pairMode || wideMode) ? TracePairs(hs, hs.rootRef, hs.bounds, q, q + 3, tMax, any, best, -1, dbg)
                           : TraceNodes(hs, int(hs.rootNode), true, q, q + 3, tMax, any, best, -1, dbg);
         if (any) occ[i] = h;
         else if (best.slot < 0) hits[i] = b200pt_hit{0xFFFFFFFFu, 0, 0, 0, 0, 0};
@@ -135,5 +149,6 @@ int main(int argc, char **argv) {
     FILE *of = fopen(argv[4], "wb");
     if (any) fwrite(occ.data(), 1, n, of); else fwrite(hits.data(), sizeof(b200pt_hit), n, of);
     fclose(of);
+    if (wideMode) fprintf(stderr, "irregular rays: %zu of %zu; wide nodes %zu, max stack %u\n", nIrregular, n, hs.wide.size(), hs.maxStackWide);
     return 0;
 }

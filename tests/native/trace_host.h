@@ -2,7 +2,9 @@
 // {ref, tMin} stack, pop-time re-check, object instances by recursion) shared by hostcheck.cpp and
 // rendercheck.cpp.  Same arithmetic headers as the CUDA kernels (isect.h, instance.h).
 #pragma once
+#include <cmath>
 #include <cstdio>
+#include <vector>
 
 #include "../../pbrt-v4_b200/csrc/instance.h"
 #include "../../pbrt-v4_b200/csrc/isect.h"
@@ -81,6 +83,88 @@ inline bool TracePairs(const HostScene &hs, int rootRef, const float *rootBox, c
         }
     }
     return any ? false : best.slot >= 0;
+}
+
+// Wide8 walk as traverse_wide.cu does it: every child box of the wide node gets the reference's slab test
+// (tMax-independent part, plus `tMin < tMax * (1 + 2^-10)`), the passing children are stacked by their rank in
+// the reference's visit order for the ray's octant (pre-set popcount; reversed when dirIsNeg[2]), and
+// `tMin < tMax` is decided at pop time.  Rays with a non-finite 1/d or origin go through TracePairs (`irregular`).
+inline bool RayIsRegular(const RayCtx &r) {
+    return std::isfinite(r.ix) && std::isfinite(r.iy) && std::isfinite(r.iz) && std::isfinite(r.ox) &&
+           std::isfinite(r.oy) && std::isfinite(r.oz);
+}
+
+// returns 0 = no hit, 1 = hit, -1 = the ray (or its image inside an instance) is irregular: redo with TracePairs
+inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, const float *o, const float *d,
+                     float &tMax, bool any, Best &best, int curInst) {
+    RayCtx r;
+    RaySetup(r, o[0], o[1], o[2], d[0], d[1], d[2]);
+    if (!RayIsRegular(r)) return -1;
+    struct E { int ref; float t; };
+    std::vector<E> stack(hs.maxStackWide + 8);
+    int sp = 0, cur = 0;
+    bool done = false;
+    auto popNext = [&]() {
+        done = true;
+        while (sp > 0) {
+            E e = stack[--sp];
+            if (e.t < tMax) { cur = e.ref; done = false; break; }
+        }
+    };
+    const bool flip = r.neg[2] != 0;
+    const int cls = (r.neg[0] ^ int(flip)) | ((r.neg[1] ^ int(flip)) << 1);
+    if (!rootBox || SlabTest(r, rootBox, rootBox + 3, tMax)) cur = rootRef; else done = true;
+    while (!done) {
+        if (cur >= 0) {
+            const Wide8 &w = hs.wide[cur];
+            const float tMaxS = B2_FMA(fabsf(tMax), 0x1p-10f, tMax);
+            unsigned H = 0;
+            float tm[8];
+            for (int i = 0; i < 8; ++i) {
+                bool ok = SlabCore(r, w.box[i], w.box[i] + 3, tm[i]) && tm[i] < tMaxS;
+                H |= unsigned(ok) << i;
+            }
+            const int nHit = __builtin_popcount(H);
+            for (int i = 0; i < 8; ++i)
+                if ((H >> i) & 1) {
+                    int rk = __builtin_popcount(H & w.pre[cls][i]);
+                    int idx = flip ? sp + rk : sp + nHit - 1 - rk;
+                    stack[idx] = E{w.ref[i], tm[i]};
+                }
+            sp += nHit;
+            popNext();
+        } else {
+            int slot = ~cur, cnt = int(hs.prims[slot].flags);
+            for (int k = 0; k < cnt; ++k, ++slot) {
+                const PrimSlot &s = hs.prims[slot];
+                if (s.mesh == kInstanceTag) {
+                    const InstanceDev &in = hs.instances[s.tri];
+                    float o2[3], d2[3], tMax2;
+                    InstanceRay(in.mInv, o[0], o[1], o[2], d[0], d[1], d[2], tMax, o2, d2, tMax2);
+                    Best sub;
+                    int h = TraceWide(hs, in.rootWide, in.rootWide < 0 ? nullptr : in.rootBox, o2, d2, tMax2, any, sub,
+                                      int(s.tri));
+                    if (h < 0) return -1;
+                    if (any && h) return 1;
+                    if (!any && sub.slot >= 0) {
+                        tMax = tMax2;
+                        best = sub;
+                    }
+                    continue;
+                }
+                float t, b0, b1, b2;
+                b0 = 0;
+                if (((s.kind & 1) ? BilinearHit(r, tMax, s.p0, s.p1, s.p2, s.p3, t, b1, b2)
+                                  : TriHit(r, tMax, s.p0, s.p1, s.p2, t, b0, b1, b2)) &&
+                    (!(s.kind & 2) || AlphaKeepsHit(r, s.p3[0]))) {
+                    if (any) return 1;
+                    tMax = t; best.slot = slot; best.inst = curInst; best.b0 = b0; best.b1 = b1; best.b2 = b2;
+                }
+            }
+            popNext();
+        }
+    }
+    return any ? 0 : int(best.slot >= 0);
 }
 
 }  // namespace b200pt

@@ -12,8 +12,9 @@ from conftest import hit_mismatches
 
 
 def run_hostcheck(binpath, P, rs, rays, layout="pair"):
-    """layout "pair" = the production PairNode walk (traverse_persist.cu), "node32" = the parity kernel's."""
-    sfx = "2" if layout == "pair" else ""
+    """layout "wide" = the production Wide8 walk (traverse_wide.cu), "pair" = the exact binary PairNode walk
+    (traverse_persist.cu; irregular rays), "node32" = the parity kernel's."""
+    sfx = {"pair": "2", "wide": "8", "node32": ""}[layout]
     rp = os.path.join(rs.dir, "rays_hc.f32")
     np.ascontiguousarray(rays, "<f4").tofile(rp)
     subprocess.check_call([binpath, rs.path, rp, "closest" + sfx, rs.dir + "/hc_hits.bin"])
@@ -39,7 +40,7 @@ CASES = {
 }
 
 
-@pytest.mark.parametrize("layout", ["pair", "node32"])
+@pytest.mark.parametrize("layout", ["wide", "pair", "node32"])
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_host_arithmetic_bit_exact(P, refrun, hostcheck_bin, case, layout):
     S = P.scenes
