@@ -1,0 +1,299 @@
+// oracle/pbrt_b200.cpp - the reference-side binding, compiled: pbrt's own parser / scene objects / film writer with
+// libb200pt.so behind them.  TEST INFRASTRUCTURE (it links the reference, oracle/_ref/libpbrt_ref.a) - this is the
+// code a pbrt maintainer would add next to wavefront/wavefront.cpp and wavefront/aggregate.cpp.
+//
+//   pbrt_b200 [--spp n] [--nthreads n] [--outfile f] scene.pbrt
+//       Level 2, the whole frame: RenderB200(BasicScene&) stands where RenderWavefront stands
+//       (wavefront/wavefront.cpp:14-70, selected at cmd/pbrt.cpp:296-299): builds the host objects as
+//       WavefrontPathIntegrator's constructor does (wavefront/integrator.cpp:89-199; the SAH BVHAggregate build
+//       stays on the host), flattens them (flatten_ref.h), hands the tables over through the C ABI
+//       (b200pt_scene_create, b200pt_render_create, b200pt_render_run), copies the device film accumulators back
+//       into the reference's own Film object (b200pt_film_read -> RGBFilm::Pixel / SpectralFilm::Pixel) and lets
+//       the reference write the image (Film::WriteImage, film.cpp:542-574; wavefront/wavefront.cpp:64-69).
+//   pbrt_b200 --wavefront [...] scene.pbrt
+//       Level 1, the intersector plug: the reference's own WavefrontPathIntegrator (its CPU kernels for camera rays,
+//       shading, lights, film) with B200Aggregate : WavefrontAggregate (wavefront/integrator.h:32-54) set in place
+//       of the CPUAggregate it constructs at wavefront/integrator.cpp:157-169.  IntersectClosest / IntersectShadow
+//       run on the GPU through b200pt_intersect_closest / b200pt_intersect_any; the SurfaceInteraction of a hit is
+//       rebuilt by the reference's own Primitive::Intersect on the ONE primitive the GPU names.
+#include "flatten_ref.h"
+
+#define private public
+#define protected public
+#include <pbrt/wavefront/aggregate.h>
+#include <pbrt/wavefront/integrator.h>
+#include <pbrt/wavefront/intersect.h>
+#undef private
+#undef protected
+#include <pbrt/util/args.h>
+#include <pbrt/util/parallel.h>
+
+#include <chrono>
+#include <unordered_map>
+
+#include "../include/b200pt.h"
+
+// ------------------------------------------------------------------ named tables in memory (the .b2rs layout)
+struct Table {
+    uint32_t dtype = 0;  // 0 f32, 1 i32, 2 u32
+    std::vector<uint32_t> dims;
+    std::vector<uint32_t> words;
+    size_t rows() const { return dims.empty() ? 0 : dims[0]; }
+    const float *f() const { return reinterpret_cast<const float *>(words.data()); }
+    const int32_t *i() const { return reinterpret_cast<const int32_t *>(words.data()); }
+    const uint32_t *u() const { return words.data(); }
+};
+struct MemTables {
+    std::map<std::string, Table> t;
+    void put(const std::string &name, uint32_t dtype, std::vector<uint32_t> dims, const void *data) {
+        Table &tb = t[name];
+        tb.dtype = dtype;
+        tb.dims = dims;
+        size_t n = 1;
+        for (uint32_t d : dims) n *= d;
+        tb.words.resize(n);
+        if (n) memcpy(tb.words.data(), data, n * 4);
+    }
+    void f32(const std::string &name, std::vector<uint32_t> dims, const std::vector<float> &v) { put(name, 0, dims, v.data()); }
+    void i32(const std::string &name, std::vector<uint32_t> dims, const std::vector<int32_t> &v) { put(name, 1, dims, v.data()); }
+    void u32(const std::string &name, std::vector<uint32_t> dims, const std::vector<uint32_t> &v) { put(name, 2, dims, v.data()); }
+    bool has(const std::string &n) const { return t.count(n) != 0; }
+    const Table &at(const std::string &n) const {
+        auto it = t.find(n);
+        if (it == t.end()) die("table missing: " + n);
+        return it->second;
+    }
+};
+
+static void check(int rc, b200pt_ctx *ctx, const char *what) {
+    if (rc != B200PT_OK) die(std::string(what) + ": " + b200pt_last_error(ctx));
+}
+
+// ------------------------------------------------------------------ tables -> include/b200pt.h descriptions
+struct Marshalled {
+    std::vector<b200pt_mesh> meshes;
+    std::vector<b200pt_instance> instances;
+    std::vector<b200pt_bvh2> bvhs;
+    b200pt_scene_desc scene{};
+    std::vector<b200pt_spectrum> spectra;
+    std::vector<b200pt_material> materials;
+    std::vector<b200pt_light> lights;
+    std::vector<b200pt_mesh_attr> attrs;
+    std::vector<b200pt_medium> media;
+    b200pt_render_desc render{};
+};
+
+static void MarshalGeometry(const MemTables &T, Marshalled &m, bool hostBvh) {
+    const Table &nv = T.at("mesh_nverts"), &nt = T.at("mesh_ntris");
+    const size_t nMesh = nv.rows();
+    const uint32_t *kind = T.has("mesh_kind") ? T.at("mesh_kind").u() : nullptr;
+    const int32_t *obj = T.at("mesh_object").i();
+    const float *alpha = T.has("mesh_alpha") ? T.at("mesh_alpha").f() : nullptr;
+    const float *P = T.at("P").f();
+    const int32_t *idx = T.at("indices").i();
+    const int32_t *pidx = T.has("patch_indices") ? T.at("patch_indices").i() : nullptr;
+    size_t vo = 0, to = 0, po = 0;
+    for (size_t i = 0; i < nMesh; ++i) {
+        b200pt_mesh me{};
+        me.object = obj[i];
+        me.n_vertices = nv.u()[i];
+        me.n_triangles = nt.u()[i];
+        me.p = P + 3 * vo;
+        const bool patch = kind && kind[i] == 1;
+        me.indices = patch ? pidx + 4 * po : idx + 3 * to;
+        me.kind = patch ? B200PT_MESH_BILINEAR : B200PT_MESH_TRIANGLES;
+        me.alpha = 1.f;
+        if (alpha && alpha[i] >= 0) {
+            me.kind |= B200PT_MESH_ALPHA;
+            me.alpha = alpha[i];
+        }
+        vo += me.n_vertices;
+        (patch ? po : to) += me.n_triangles;
+        m.meshes.push_back(me);
+    }
+    if (T.has("instance_object")) {
+        const Table &io = T.at("instance_object");
+        const float *im = T.at("instance_m").f(), *imi = T.at("instance_minv").f();
+        for (size_t k = 0; k < io.rows(); ++k) {
+            b200pt_instance in{};
+            in.object = uint32_t(io.i()[k]);
+            memcpy(in.render_from_instance, im + 16 * k, 64);
+            memcpy(in.instance_from_render, imi + 16 * k, 64);
+            m.instances.push_back(in);
+        }
+    }
+    if (hostBvh && T.has("bvh_nodes")) {  // the host's own BVHAggregate trees (LinearBVHNode layout)
+        const Table &bn = T.at("bvh_nodes"), &bp = T.at("bvh_prims");
+        m.bvhs.push_back(b200pt_bvh2{-1, uint32_t(bn.rows()), uint32_t(bp.rows()), bn.u(), bp.u()});
+        for (int k = 0; T.has("obj_bvh_nodes_" + std::to_string(k)); ++k) {
+            const Table &on = T.at("obj_bvh_nodes_" + std::to_string(k)), &op = T.at("obj_bvh_prims_" + std::to_string(k));
+            m.bvhs.push_back(b200pt_bvh2{k, uint32_t(on.rows()), uint32_t(op.rows()), on.u(), op.u()});
+        }
+    }
+    m.scene.n_meshes = uint32_t(m.meshes.size());
+    m.scene.meshes = m.meshes.data();
+    m.scene.n_instances = uint32_t(m.instances.size());
+    m.scene.instances = m.instances.data();
+    m.scene.n_bvhs = uint32_t(m.bvhs.size());
+    m.scene.bvhs = m.bvhs.data();
+}
+
+static void MarshalRender(const MemTables &T, Marshalled &m) {
+    b200pt_render_desc &r = m.render;
+    r.camera_type = T.at("camera_type").u()[0];
+    memcpy(r.render_from_camera, T.at("render_from_camera").f(), 64);
+    if (r.camera_type == 0) {
+        memcpy(r.camera_from_raster, T.at("camera_from_raster").f(), 64);
+        r.lens_radius = T.at("camera_params").f()[0];
+        r.focal_distance = T.at("camera_params").f()[1];
+    } else {
+        const Table &lens = T.at("camera_lens"), &pupil = T.at("camera_exit_pupil");
+        r.n_lens_elements = uint32_t(lens.rows());
+        r.lens_elements = lens.f();
+        r.n_exit_pupil_bounds = uint32_t(pupil.rows());
+        r.exit_pupil_bounds = pupil.f();
+        memcpy(r.physical_extent, T.at("camera_extent").f(), 16);
+        r.film_diagonal = T.at("camera_extent").f()[4];
+        if (r.camera_type == 2 && T.has("camera_lens_transforms")) r.lens_element_transforms = T.at("camera_lens_transforms").f();
+        if (r.camera_type == 2 && T.has("microlens_lens")) {
+            const int32_t *mi = T.at("microlens_ints").i();
+            r.n_microlens_elements = uint32_t(T.at("microlens_lens").rows());
+            r.microlens_elements = T.at("microlens_lens").f();
+            r.microlens_element_transforms = T.at("microlens_transforms").f();
+            r.microlens_offsets = T.at("microlens_offsets").f();
+            r.microlens_dims[0] = mi[0];
+            r.microlens_dims[1] = mi[1];
+            r.microlens_simulation_radius = mi[2];
+            r.microlens_offset_from_sensor = T.at("microlens_params").f()[0];
+        }
+    }
+    r.film_type = T.at("film_type").u()[0];
+    if (r.film_type == 1) {
+        const float *fs = T.at("film_spectral").f();
+        r.n_buckets = uint32_t(fs[0]);
+        r.lambda_min = fs[1];
+        r.lambda_max = fs[2];
+    }
+    const int32_t *fi = T.at("film_ints").i();
+    memcpy(r.pixel_bounds, fi, 16);
+    memcpy(r.full_resolution, fi + 4, 8);
+    const float *fp = T.at("film_params").f();
+    r.filter_radius[0] = fp[0];
+    r.filter_radius[1] = fp[1];
+    r.imaging_ratio = fp[2];
+    r.max_component_value = fp[3];
+    memcpy(r.output_rgb_from_sensor_rgb, T.at("film_matrix").f(), 36);
+    memcpy(r.sensor_spectrum, T.at("film_sensor").i(), 12);
+    const int32_t *s = T.at("sampler").i();
+    r.sampler_type = uint32_t(s[0]);
+    r.samples_per_pixel = s[1];
+    r.seed = s[2];
+    r.randomize = uint32_t(s[3]);
+    const int32_t *ig = T.at("integrator").i();
+    r.max_depth = ig[0];
+    r.regularize = uint32_t(ig[1]);
+    r.light_sampler = uint32_t(ig[2]);
+    r.integrator_type = T.at("integrator_type").u()[0];
+    const Table &sv = T.at("spectra_values");
+    m.spectra.resize(std::max<size_t>(1, sv.rows()));
+    for (size_t i = 0; i < sv.rows(); ++i) {
+        m.spectra[i].interp = T.at("spectra_interp").u()[i];
+        memcpy(m.spectra[i].values, sv.f() + 311 * i, 311 * 4);
+    }
+    const Table &mi = T.at("materials_i"), &mf = T.at("materials_f");
+    m.materials.resize(std::max<size_t>(1, mi.rows()));
+    for (size_t i = 0; i < mi.rows(); ++i) {
+        const int32_t *rec = mi.i() + 5 * i;
+        m.materials[i].type = rec[0] >= 0 ? uint32_t(rec[0]) : 0u;
+        memcpy(m.materials[i].spectrum, rec + 1, 16);
+        memcpy(m.materials[i].params, mf.f() + 8 * i, 32);
+    }
+    const Table &li = T.at("lights_i"), &lf = T.at("lights_f");
+    m.lights.resize(std::max<size_t>(1, li.rows()));
+    for (size_t i = 0; i < li.rows(); ++i) {
+        const int32_t *a = li.i() + 7 * i;
+        const float *b = lf.f() + 6 * i;
+        b200pt_light &L = m.lights[i];
+        L.mesh = uint32_t(std::max(a[0], 0));
+        L.tri = uint32_t(std::max(a[1], 0));
+        L.spectrum = a[2];
+        L.scale = b[0];
+        L.two_sided = uint32_t(a[3]);
+        L.cos_falloff_end = b[1];
+        L.tan_falloff_end = b[2];
+        L.normalize_falloff_end = b[3];
+        L.alias_q = b[4];
+        L.alias_p = b[5];
+        L.alias = a[4];
+        L.type = uint32_t(a[6]);
+    }
+    const Table &ma = T.at("mesh_attr");
+    const size_t nMesh = ma.rows();
+    m.attrs.resize(std::max<size_t>(1, nMesh));
+    const uint32_t *hasN = T.has("mesh_has_n") ? T.at("mesh_has_n").u() : nullptr;
+    const uint32_t *hasUV = T.has("mesh_has_uv") ? T.at("mesh_has_uv").u() : nullptr;
+    const uint32_t *kind = T.has("mesh_kind") ? T.at("mesh_kind").u() : nullptr;
+    const uint32_t *ntris = T.at("mesh_ntris").u();
+    size_t nAt = 0, uvAt = 0;
+    for (size_t i = 0; i < nMesh; ++i) {
+        const int32_t *a = ma.i() + 3 * i;
+        b200pt_mesh_attr &A = m.attrs[i];
+        A.material = a[0];
+        A.light_first = a[1];
+        A.flip_normal = uint32_t(std::max(a[2], 0));
+        A.corner_n = A.corner_uv = nullptr;
+        if (hasN && hasN[i]) {
+            const size_t per = (kind && kind[i] == 1) ? 4 : 3;
+            A.corner_n = T.at("corner_n").f() + 3 * nAt;
+            nAt += per * ntris[i];
+        }
+        if (hasUV && hasUV[i]) {
+            A.corner_uv = T.at("corner_uv").f() + 2 * uvAt;
+            uvAt += 3 * size_t(ntris[i]);
+        }
+    }
+    r.n_spectra = uint32_t(sv.rows());
+    r.n_materials = uint32_t(mi.rows());
+    r.n_lights = uint32_t(li.rows());
+    r.n_meshes = uint32_t(nMesh);
+    r.spectra = m.spectra.data();
+    r.materials = m.materials.data();
+    r.lights = m.lights.data();
+    r.meshes = m.attrs.data();
+    r.camera_medium = -1;
+    if (r.integrator_type == 1) {
+        const Table &mdi = T.at("media_i"), &mdf = T.at("media_f");
+        m.media.resize(std::max<size_t>(1, mdi.rows()));
+        for (size_t k = 0; k < mdi.rows(); ++k) {
+            const int32_t *a = mdi.i() + 9 * k;
+            const float *b = mdf.f() + 39 * k;
+            b200pt_medium &M = m.media[k];
+            memset(&M, 0, sizeof M);
+            M.type = uint32_t(a[0]);
+            M.sigma_a = a[1];
+            M.sigma_s = a[2];
+            M.nx = a[3];
+            M.ny = a[4];
+            M.nz = a[5];
+            memcpy(M.mres, a + 6, 12);
+            M.g = b[0];
+            memcpy(M.bounds, b + 1, 24);
+            memcpy(M.medium_from_render, b + 7, 64);
+            memcpy(M.render_from_medium, b + 23, 64);
+            if (M.type == 1) {
+                M.density = T.at("medium_density_" + std::to_string(k)).f();
+                M.majorants = T.at("medium_majorants_" + std::to_string(k)).f();
+            }
+        }
+        r.n_media = uint32_t(mdi.rows());
+        r.media = m.media.data();
+        r.mesh_media = T.at("mesh_media").i();
+        r.camera_medium = T.at("camera_medium").i()[0];
+    }
+    if (r.light_sampler == 2) {
+        r.n_light_bvh_nodes = uint32_t(T.at("lightbvh_nodes").rows());
+        memcpy(r.light_bvh_bounds, T.at("lightbvh_bounds").f(), 24);
+        r.light_bvh_nodes = T.at("lightbvh_nodes").u();
+        r.light_bit_trails = T.at("lightbvh_trails").u();
+    }
+}

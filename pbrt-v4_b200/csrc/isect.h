@@ -141,6 +141,20 @@ B2_HD bool SlabCore(const RayCtx &r, const float *bmin, const float *bmax, float
     return ok & (tMax > 0);
 }
 
+// The same test for a REGULAR ray (1/d and o finite, so no product is NaN) with the near / far planes already
+// picked (near = dirIsNeg ? pMax : pMin per axis, as the reference picks them).  Without NaNs the reference's chain
+// of comparisons and conditional updates is max(near products) <= min(padded far products) && min(...) > 0: same
+// products, same roundings, same boolean; tMinOut equal to SlabCore's up to the sign of a zero.  (If a far product
+// is negative its padded value can drop below the near one; then min(...) < 0 and both forms reject.)  An empty
+// slot's box (+inf, -inf) gives near = +inf, far = -inf: rejected, no NaN.
+B2_HD bool SlabPlanesRegular(const RayCtx &r, float nx, float ny, float nz, float fx, float fy, float fz, float &tMinOut) {
+    float tMin = fmaxf(fmaxf(B2_MUL(B2_SUB(nx, r.ox), r.ix), B2_MUL(B2_SUB(ny, r.oy), r.iy)), B2_MUL(B2_SUB(nz, r.oz), r.iz));
+    float tMax = fminf(fminf(B2_MUL(B2_MUL(B2_SUB(fx, r.ox), r.ix), kSlabPad), B2_MUL(B2_MUL(B2_SUB(fy, r.oy), r.iy), kSlabPad)),
+                       B2_MUL(B2_MUL(B2_SUB(fz, r.oz), r.iz), kSlabPad));
+    tMinOut = tMin;
+    return (tMin <= tMax) & (tMax > 0);
+}
+
 B2_HD bool SlabTest(const RayCtx &r, const float *bmin, const float *bmax, float raytMax) {
     float tMin;
     return SlabCore(r, bmin, bmax, tMin) & (tMin < raytMax);

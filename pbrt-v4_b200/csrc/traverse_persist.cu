@@ -101,9 +101,13 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
         // terms: that ray merely takes the exact kernel too)
         return ((fabsf(r.ix) + fabsf(r.iy)) + (fabsf(r.iz) + fabsf(r.ox)) + (fabsf(r.oy) + fabsf(r.oz))) < INFINITY;
     };
+    int offNear[3] = {0, 32, 64};  // WIDE: byte offset of the near plane of each axis inside a node
     auto setOctant = [&]() {
         flip = r.neg[2] != 0;
         cls = (r.neg[0] ^ int(flip)) | ((r.neg[1] ^ int(flip)) << 1);
+        offNear[0] = r.neg[0] ? 96 : 0;
+        offNear[1] = r.neg[1] ? 128 : 32;
+        offNear[2] = r.neg[2] ? 160 : 64;
     };
     // hands the ray over to the exact binary kernel
     auto giveUp = [&]() {
@@ -210,27 +214,15 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                     const float tMaxS = __fmaf_rn(fabsf(tMax), 0x1p-10f, tMax);
                     unsigned H = 0;
                     float tm[8];
-                    Node8f a0 = Load256(np), b0 = Load256(np + 32), c0 = Load256(np + 64);
-                    Node8f a1 = Load256(np + 96), b1 = Load256(np + 128), c1 = Load256(np + 160);
-                    {
-                        const float bx[24] = {a0.v[0], a0.v[1], a0.v[2], a0.v[3], a0.v[4], a0.v[5], a0.v[6], a0.v[7],
-                                              b0.v[0], b0.v[1], b0.v[2], b0.v[3], b0.v[4], b0.v[5], b0.v[6], b0.v[7],
-                                              c0.v[0], c0.v[1], c0.v[2], c0.v[3], c0.v[4], c0.v[5], c0.v[6], c0.v[7]};
+                    // one 32-byte load per plane of the eight children; the near / far plane of each axis by address
+                    const Node8f nx = Load256(np + offNear[0]), ny = Load256(np + offNear[1]), nz = Load256(np + offNear[2]);
+                    const Node8f fx = Load256(np + (96 - offNear[0])), fy = Load256(np + (160 - offNear[1])),
+                                 fz = Load256(np + (224 - offNear[2]));
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            bool ok = SlabCore(r, bx + 6 * j, bx + 6 * j + 3, tm[j]) & (tm[j] < tMaxS);
-                            H |= unsigned(ok) << j;
-                        }
-                    }
-                    {
-                        const float bx[24] = {a1.v[0], a1.v[1], a1.v[2], a1.v[3], a1.v[4], a1.v[5], a1.v[6], a1.v[7],
-                                              b1.v[0], b1.v[1], b1.v[2], b1.v[3], b1.v[4], b1.v[5], b1.v[6], b1.v[7],
-                                              c1.v[0], c1.v[1], c1.v[2], c1.v[3], c1.v[4], c1.v[5], c1.v[6], c1.v[7]};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            bool ok = SlabCore(r, bx + 6 * j, bx + 6 * j + 3, tm[4 + j]) & (tm[4 + j] < tMaxS);
-                            H |= unsigned(ok) << (4 + j);
-                        }
+                    for (int i = 0; i < 8; ++i) {
+                        bool ok = SlabPlanesRegular(r, nx.v[i], ny.v[i], nz.v[i], fx.v[i], fy.v[i], fz.v[i], tm[i]) &
+                                  (tm[i] < tMaxS);
+                        H |= unsigned(ok) << i;
                     }
                     if (H) {
                         Node8f rf = Load256(np + 192);
@@ -238,16 +230,31 @@ TraversePersistKernel(DeviceScene sc, const float *__restrict__ rays, int n, b20
                         const int nHit = __popc(H);
                         // rank in the reference's visit order = hits among the slots visited before this one; the
                         // first to be visited ends on top of the stack (reversed order when dirIsNeg[2])
-                        const int base = flip ? sp : sp + nHit - 1;
+                        if (sp + nHit <= kSmemDepth) {
+                            int2 *top = stack + (flip ? sp : sp + nHit - 1) * kBlock;
+                            const int step = flip ? kBlock : -kBlock;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            if ((H >> i) & 1u) {
-                                const unsigned before = ((i < 4 ? pre.x : pre.y) >> (8 * (i & 3))) & 0xffu;
-                                const int rk = __popc(H & before);
-                                const int idx = flip ? base + rk : base - rk;
-                                const int2 e = make_int2(__float_as_int(rf.v[i]), __float_as_int(tm[i]));
-                                if (idx < kSmemDepth) stack[idx * kBlock] = e;
-                                else deep[idx - kSmemDepth] = e;
+                            for (int i = 0; i < 8; ++i) {
+                                const unsigned before = ((i < 4 ? pre.x : pre.y) >> (8 * (i & 3))) & H;
+                                int2 *dst = top + __popc(before & 0xffu) * step;
+                                if ((H >> i) & 1u) *dst = make_int2(__float_as_int(rf.v[i]), __float_as_int(tm[i]));
+                            }
+                        } else {
+                            const int base = flip ? sp : sp + nHit - 1;
+#pragma unroll 1
+                            for (int i = 0; i < 8; ++i) {
+                                if ((H >> i) & 1u) {
+                                    const unsigned before = ((i < 4 ? pre.x : pre.y) >> (8 * (i & 3))) & 0xffu;
+                                    const int rk = __popc(H & before);
+                                    const int idx = flip ? base + rk : base - rk;
+                                    float refBits = i == 0 ? rf.v[0] : i == 1 ? rf.v[1] : i == 2 ? rf.v[2] : i == 3 ? rf.v[3]
+                                                  : i == 4 ? rf.v[4] : i == 5 ? rf.v[5] : i == 6 ? rf.v[6] : rf.v[7];
+                                    float tBits = i == 0 ? tm[0] : i == 1 ? tm[1] : i == 2 ? tm[2] : i == 3 ? tm[3]
+                                                : i == 4 ? tm[4] : i == 5 ? tm[5] : i == 6 ? tm[6] : tm[7];
+                                    const int2 e = make_int2(__float_as_int(refBits), __float_as_int(tBits));
+                                    if (idx < kSmemDepth) stack[idx * kBlock] = e;
+                                    else deep[idx - kSmemDepth] = e;
+                                }
                             }
                         }
                         sp += nHit;

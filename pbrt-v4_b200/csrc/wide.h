@@ -32,7 +32,10 @@
 namespace b200pt {
 
 struct alignas(128) Wide8 {
-    float box[8][6];    // child i: pMin xyz, pMax xyz (empty slot: +inf / -inf, never passes)
+    // plane p of child i: p = 0..2 pMin.xyz, 3..5 pMax.xyz (empty slot: +inf / -inf, never passes).  One 32-byte
+    // load per plane; the ray's near plane along axis k is plane (dirIsNeg[k] ? 3 + k : k) - chosen by ADDRESS, so
+    // the kernel does the reference's `dirIsNeg ? pMax : pMin` selection (util/vecmath.h:1580-1586) with no select
+    float plane[6][8];
     int32_t ref[8];     // >= 0: Wide8 index; < 0: leaf, first PrimSlot = ~ref (count in that slot's `flags`)
     uint8_t pre[4][8];  // [negx | negy << 1][slot] = bit mask of the slots visited before `slot` (negz = 0)
 };

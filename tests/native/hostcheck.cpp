@@ -149,6 +149,12 @@ int main(int argc, char **argv) {
     FILE *of = fopen(argv[4], "wb");
     if (any) fwrite(occ.data(), 1, n, of); else fwrite(hits.data(), sizeof(b200pt_hit), n, of);
     fclose(of);
-    if (wideMode) fprintf(stderr, "irregular rays: %zu of %zu; wide nodes %zu, max stack %u\n", nIrregular, n, hs.wide.size(), hs.maxStackWide);
+    if (wideMode) {
+        const WideCounters &c = WideStats();
+        fprintf(stderr, "irregular rays: %zu of %zu; wide nodes %zu, max stack %u; per ray: %.2f wide visits (%.2f of 8 slots used, "
+                "%.2f children entered), %.2f leaves, %.2f prims\n", nIrregular, n, hs.wide.size(), hs.maxStackWide,
+                double(c.visits) / n, c.visits ? double(c.children) / c.visits : 0., c.visits ? double(c.childHits) / c.visits : 0.,
+                double(c.leaves) / n, double(c.prims) / n);
+    }
     return 0;
 }

@@ -89,6 +89,14 @@ inline bool TracePairs(const HostScene &hs, int rootRef, const float *rootBox, c
 // (tMax-independent part, plus `tMin < tMax * (1 + 2^-10)`), the passing children are stacked by their rank in
 // the reference's visit order for the ray's octant (pre-set popcount; reversed when dirIsNeg[2]), and
 // `tMin < tMax` is decided at pop time.  Rays with a non-finite 1/d or origin go through TracePairs (`irregular`).
+struct WideCounters {
+    unsigned long long visits = 0, childHits = 0, leaves = 0, prims = 0, children = 0;
+};
+inline WideCounters &WideStats() {
+    static WideCounters c;
+    return c;
+}
+
 inline bool RayIsRegular(const RayCtx &r) {
     return std::isfinite(r.ix) && std::isfinite(r.iy) && std::isfinite(r.iz) && std::isfinite(r.ox) &&
            std::isfinite(r.oy) && std::isfinite(r.oz);
@@ -121,10 +129,16 @@ inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, con
             unsigned H = 0;
             float tm[8];
             for (int i = 0; i < 8; ++i) {
-                bool ok = SlabCore(r, w.box[i], w.box[i] + 3, tm[i]) && tm[i] < tMaxS;
+                // near / far plane of each axis as the kernel picks them by address
+                const int nxp = r.neg[0] ? 3 : 0, nyp = r.neg[1] ? 4 : 1, nzp = r.neg[2] ? 5 : 2;
+                bool ok = SlabPlanesRegular(r, w.plane[nxp][i], w.plane[nyp][i], w.plane[nzp][i], w.plane[3 - nxp][i],
+                                            w.plane[5 - nyp][i], w.plane[7 - nzp][i], tm[i]) && tm[i] < tMaxS;
                 H |= unsigned(ok) << i;
             }
             const int nHit = __builtin_popcount(H);
+            WideStats().visits++;
+            WideStats().childHits += nHit;
+            for (int i = 0; i < 8; ++i) WideStats().children += w.ref[i] != kWideEmpty;
             for (int i = 0; i < 8; ++i)
                 if ((H >> i) & 1) {
                     int rk = __builtin_popcount(H & w.pre[cls][i]);
@@ -135,6 +149,8 @@ inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, con
             popNext();
         } else {
             int slot = ~cur, cnt = int(hs.prims[slot].flags);
+            WideStats().leaves++;
+            WideStats().prims += cnt;
             for (int k = 0; k < cnt; ++k, ++slot) {
                 const PrimSlot &s = hs.prims[slot];
                 if (s.mesh == kInstanceTag) {

@@ -60,3 +60,22 @@ def test_degenerate_inputs(P):
     boxes = np.concatenate([c, c + np.float32(0.01)], axis=1)
     nodes, order = P.capi.bvh2_build(boxes, 1)
     assert (nodes["nprims"][nodes["nprims"] > 0] == 1).all() and len(nodes) == 127
+
+
+def test_parallel_build_is_the_serial_build(P, monkeypatch):
+    """The multi-threaded build (serial top, subtrees on worker threads, one depth-first layout) gives the
+    single-threaded build's tree byte for byte, whatever the thread count."""
+    import time
+    sc = P.scenes.random_soup(400000, seed=21, s=0.01)
+    boxes = sc.triangle_boxes()
+    monkeypatch.setenv("B200PT_BUILD_THREADS", "1")
+    t0 = time.perf_counter()
+    n1, o1 = P.capi.bvh2_build(boxes, 4)
+    t1 = time.perf_counter() - t0
+    for threads in ("3", "8"):
+        monkeypatch.setenv("B200PT_BUILD_THREADS", threads)
+        t0 = time.perf_counter()
+        n2, o2 = P.capi.bvh2_build(boxes, 4)
+        tp = time.perf_counter() - t0
+        assert n1.tobytes() == n2.tobytes() and np.array_equal(o1, o2)
+        print(f"build 400K: 1 thread {t1:.3f} s, {threads} threads {tp:.3f} s")
