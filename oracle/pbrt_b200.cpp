@@ -297,3 +297,415 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         r.light_bit_trails = T.at("lightbvh_trails").u();
     }
 }
+
+// ------------------------------------------------------------------ Level 2: the frame
+static void RenderB200(BasicScene &scene, int device, bool hostBvh) {
+    using clk = std::chrono::steady_clock;
+    RefObjects ro;
+    CreateRefObjects(scene, ro);
+    MemTables T;
+    FlattenScene(ro, T, hostBvh);
+    Marshalled m;
+    MarshalGeometry(T, m, hostBvh);
+    MarshalRender(T, m);
+
+    b200pt_ctx *ctx = nullptr;
+    if (b200pt_context_create(device, &ctx) != B200PT_OK) die(std::string("b200pt_context_create: ") + b200pt_last_error(nullptr));
+    b200pt_scene *sc = nullptr;
+    check(b200pt_scene_create(ctx, &m.scene, &sc), ctx, "b200pt_scene_create");
+    b200pt_render *rd = nullptr;
+    check(b200pt_render_create(sc, &m.render, &rd), ctx, "b200pt_render_create");
+    auto t0 = clk::now();
+    check(b200pt_render_run(rd, 0, m.render.samples_per_pixel, 1), ctx, "b200pt_render_run");
+    check(b200pt_context_sync(ctx), ctx, "b200pt_context_sync");
+    const double seconds = std::chrono::duration<double>(clk::now() - t0).count();
+
+    // the device film accumulators, back into the reference's Film object (row major over pixelBounds, Array2D order)
+    Bounds2i pb = ro.film.PixelBounds();
+    const size_t nPix = size_t(pb.Area());
+    const size_t nB = m.render.film_type == 1 ? m.render.n_buckets : 0;
+    std::vector<double> acc(nPix * (4 + 2 * nB));
+    check(b200pt_film_read(rd, acc.data()), ctx, "b200pt_film_read");
+    const int W = pb.pMax.x - pb.pMin.x;
+    if (RGBFilm *rf = ro.film.CastOrNullptr<RGBFilm>()) {
+        for (Point2i p : pb) {
+            const size_t k = size_t(p.y - pb.pMin.y) * W + (p.x - pb.pMin.x);
+            auto &px = rf->pixels[p];
+            for (int c = 0; c < 3; ++c) px.rgbSum[c] = acc[4 * k + c];
+            px.weightSum = acc[4 * k + 3];
+        }
+    } else if (SpectralFilm *sf = ro.film.CastOrNullptr<SpectralFilm>()) {
+        const double *bs = acc.data() + 4 * nPix, *ws = bs + nB * nPix;
+        for (Point2i p : pb) {
+            const size_t k = size_t(p.y - pb.pMin.y) * W + (p.x - pb.pMin.x);
+            auto &px = sf->pixels[p];
+            for (int c = 0; c < 3; ++c) px.rgbSum[c] = acc[4 * k + c];
+            px.rgbWeightSum = acc[4 * k + 3];
+            for (size_t b = 0; b < nB; ++b) {
+                px.bucketSums[b] = bs[b * nPix + k];
+                px.weightSums[b] = ws[b * nPix + k];
+            }
+        }
+    } else
+        die("RenderB200: film type not handled");
+    b200pt_render_stats st{};
+    b200pt_render_get_stats(rd, &st);
+    fprintf(stderr, "pbrt_b200: %llu samples in %.3f s (gpu %.1f ms, %u launches, %llu + %llu rays)\n",
+            (unsigned long long)st.samples, seconds, st.gpu_ms, st.kernel_launches, (unsigned long long)st.closest_rays,
+            (unsigned long long)st.shadow_rays);
+    b200pt_render_destroy(rd);
+    b200pt_scene_destroy(sc);
+    b200pt_context_destroy(ctx);
+
+    ImageMetadata metadata;  // wavefront/wavefront.cpp:64-69
+    ro.camera.InitMetadata(&metadata);
+    metadata.renderTimeSeconds = seconds;
+    metadata.samplesPerPixel = ro.sampler.SamplesPerPixel();
+    ro.film.WriteImage(metadata);
+}
+
+// ------------------------------------------------------------------ Level 1: the intersector plug
+class B200Aggregate : public WavefrontAggregate {
+  public:
+    // `accel`: the aggregate BasicScene::CreateAggregate built (the host keeps parsing and the SAH build);
+    // its trees are handed over as they are, so every ray visits what the reference's BVHAggregate visits.
+    B200Aggregate(Primitive accel, int device) : aggregate(accel) {
+        if (!accel.Is<BVHAggregate>()) die("B200Aggregate: top-level aggregate is not a BVH");
+        const BVHAggregate *bvh = accel.Cast<BVHAggregate>();
+        const auto &triMeshes = *Triangle::allMeshes;
+        nTriMeshes = triMeshes.size();
+        const size_t nPatchMeshes = BilinearPatch::allMeshes ? BilinearPatch::allMeshes->size() : 0;
+        std::vector<int32_t> meshObject(nTriMeshes + nPatchMeshes, -2);  // -2 = not referenced by the aggregate
+        std::vector<float> meshAlpha(nTriMeshes + nPatchMeshes, -1.f);
+        auto visit = [&](const Primitive &p, int object, std::vector<uint32_t> &out) {
+            Shape shape;
+            if (const SimplePrimitive *sp = p.CastOrNullptr<SimplePrimitive>()) shape = sp->shape;
+            else if (const GeometricPrimitive *gp = p.CastOrNullptr<GeometricPrimitive>()) {
+                shape = gp->shape;
+                if (gp->alpha) {
+                    const FloatConstantTexture *ct = gp->alpha.CastOrNullptr<FloatConstantTexture>();
+                    if (!ct || !shape.Is<Triangle>()) die("B200Aggregate: only constant alpha textures on triangle meshes");
+                    meshAlpha[shape.Cast<Triangle>()->meshIndex] = ct->Evaluate(TextureEvalContext());
+                }
+            } else
+                die("B200Aggregate: only triangle / bilinear patch primitives and object instances");
+            uint32_t m, k, kind;
+            if (const Triangle *t = shape.CastOrNullptr<Triangle>()) {
+                m = uint32_t(t->meshIndex);
+                k = uint32_t(t->triIndex);
+                kind = 0;
+            } else if (const BilinearPatch *bp = shape.CastOrNullptr<BilinearPatch>()) {
+                m = uint32_t(nTriMeshes + bp->meshIndex);
+                k = uint32_t(bp->blpIndex);
+                kind = 2;
+            } else
+                die("B200Aggregate: only triangles and bilinear patches");
+            meshObject[m] = object;
+            out.insert(out.end(), {kind, m, k});
+            primOf[uint64_t(m) << 32 | k] = p;
+        };
+        std::vector<uint32_t> topPrims;
+        std::vector<std::vector<uint32_t>> objPrims;
+        std::vector<std::vector<uint32_t>> objNodes;
+        std::map<const void *, int> objectId;
+        std::map<int, std::pair<int, const TransformedPrimitive *>> byId;
+        for (const Primitive &p : bvh->primitives) {
+            const TransformedPrimitive *tp = p.CastOrNullptr<TransformedPrimitive>();
+            if (!tp) {
+                visit(p, -1, topPrims);
+                continue;
+            }
+            const void *key = tp->primitive.ptr();
+            if (!objectId.count(key)) {
+                const int id = int(objectId.size());
+                objectId[key] = id;
+                objPrims.emplace_back();
+                objNodes.emplace_back();
+                if (const BVHAggregate *ob = tp->primitive.CastOrNullptr<BVHAggregate>()) {
+                    for (const Primitive &q : ob->primitives) visit(q, id, objPrims[id]);
+                    const int nn = countNodes(ob->nodes);
+                    objNodes[id].resize(size_t(nn) * 8);
+                    memcpy(objNodes[id].data(), ob->nodes, size_t(nn) * 32);
+                } else {  // a one-primitive object has no BVH (scene.cpp:1551): a one-leaf tree of its bounds
+                    visit(tp->primitive, id, objPrims[id]);
+                    LinearBVHNode leaf;
+                    memset(&leaf, 0, sizeof leaf);
+                    leaf.bounds = tp->primitive.Bounds();
+                    leaf.nPrimitives = 1;
+                    objNodes[id].resize(8);
+                    memcpy(objNodes[id].data(), &leaf, 32);
+                }
+            }
+            topPrims.insert(topPrims.end(), {1u, uint32_t(tp->instanceId), 0u});
+            byId[tp->instanceId] = {objectId[key], tp};
+        }
+        // meshes the aggregate refers to, renumbered densely; refMesh maps back to the reference's numbering
+        std::vector<b200pt_mesh> used;
+        std::vector<uint32_t> remap(meshObject.size(), 0xFFFFFFFFu);
+        for (size_t mi = 0; mi < meshObject.size(); ++mi) {
+            if (meshObject[mi] == -2) continue;
+            b200pt_mesh me;
+            memset(&me, 0, sizeof me);
+            me.object = meshObject[mi];
+            me.alpha = 1.f;
+            if (mi < nTriMeshes) {
+                const TriangleMesh *tm = triMeshes[mi];
+                me.n_vertices = uint32_t(tm->nVertices);
+                me.n_triangles = uint32_t(tm->nTriangles);
+                me.p = reinterpret_cast<const float *>(tm->p);  // Point3f = 3 floats
+                me.indices = tm->vertexIndices;
+                if (meshAlpha[mi] >= 0) {
+                    me.kind = B200PT_MESH_ALPHA;
+                    me.alpha = meshAlpha[mi];
+                }
+            } else {
+                const BilinearPatchMesh *bm = (*BilinearPatch::allMeshes)[mi - nTriMeshes];
+                me.n_vertices = uint32_t(bm->nVertices);
+                me.n_triangles = uint32_t(bm->nPatches);
+                me.p = reinterpret_cast<const float *>(bm->p);
+                me.indices = bm->vertexIndices;
+                me.kind = B200PT_MESH_BILINEAR;
+            }
+            remap[mi] = uint32_t(used.size());
+            refMesh.push_back(uint32_t(mi));
+            used.push_back(me);
+        }
+        auto renumber = [&](std::vector<uint32_t> &pr) {
+            for (size_t i = 0; i < pr.size(); i += 3)
+                if (pr[i] != 1) pr[i + 1] = remap[pr[i + 1]];
+        };
+        renumber(topPrims);
+        for (auto &op : objPrims) renumber(op);
+        std::vector<b200pt_instance> insts;
+        for (size_t k = 0; k < byId.size(); ++k) {
+            auto it = byId.find(int(k) + 1);
+            if (it == byId.end()) die("B200Aggregate: instance ids are not 1..n");
+            b200pt_instance in{};
+            in.object = uint32_t(it->second.first);
+            std::vector<float> a = Mat(it->second.second->renderFromPrimitive->GetMatrix()),
+                               b = Mat(it->second.second->renderFromPrimitive->GetInverseMatrix());
+            memcpy(in.render_from_instance, a.data(), 64);
+            memcpy(in.instance_from_render, b.data(), 64);
+            insts.push_back(in);
+            instances.push_back(it->second.second);
+        }
+        const int nTop = countNodes(bvh->nodes);
+        std::vector<b200pt_bvh2> bvhs;
+        bvhs.push_back(b200pt_bvh2{-1, uint32_t(nTop), uint32_t(topPrims.size() / 3), bvh->nodes, topPrims.data()});
+        for (size_t k = 0; k < objNodes.size(); ++k)
+            bvhs.push_back(b200pt_bvh2{int32_t(k), uint32_t(objNodes[k].size() / 8), uint32_t(objPrims[k].size() / 3),
+                                       objNodes[k].data(), objPrims[k].data()});
+        b200pt_scene_desc desc{};
+        desc.n_meshes = uint32_t(used.size());
+        desc.meshes = used.data();
+        desc.n_instances = uint32_t(insts.size());
+        desc.instances = insts.data();
+        desc.n_bvhs = uint32_t(bvhs.size());
+        desc.bvhs = bvhs.data();
+        if (b200pt_context_create(device, &ctx) != B200PT_OK)
+            die(std::string("b200pt_context_create: ") + b200pt_last_error(nullptr));
+        check(b200pt_scene_create(ctx, &desc, &scene), ctx, "b200pt_scene_create");
+    }
+    ~B200Aggregate() override {
+        fprintf(stderr, "B200Aggregate: %llu closest + %llu shadow rays on the GPU, %llu single-ray calls, %llu t mismatches\n",
+                (unsigned long long)nClosest.load(), (unsigned long long)nShadow.load(), (unsigned long long)nSingle.load(),
+                (unsigned long long)nMismatch.load());
+        b200pt_scene_destroy(scene);
+        b200pt_context_destroy(ctx);
+    }
+
+    Bounds3f Bounds() const override {
+        float b[6];
+        b200pt_scene_bounds(scene, b);
+        return Bounds3f(Point3f(b[0], b[1], b[2]), Point3f(b[3], b[4], b[5]));
+    }
+
+    // The SurfaceInteraction of a GPU hit: the reference's own Primitive::Intersect on the one primitive the hit
+    // names (GeometricPrimitive::Intersect sets material / area light / medium interface, cpu/primitive.cpp:50-95;
+    // an instance goes through TransformedPrimitive::Intersect's steps, cpu/primitive.cpp:112-127).
+    pstd::optional<ShapeIntersection> Rebuild(const Ray &ray, Float tMax, const b200pt_hit &h) const {
+        auto it = primOf.find(uint64_t(refMesh[h.mesh]) << 32 | h.prim);
+        if (it == primOf.end()) die("B200Aggregate: hit on an unknown primitive");
+        pstd::optional<ShapeIntersection> si;
+        if (h.instance == 0) {
+            si = it->second.Intersect(ray, tMax);
+        } else {
+            const TransformedPrimitive *tp = instances[h.instance - 1];
+            Float tm = tMax;
+            Ray r = tp->renderFromPrimitive->ApplyInverse(ray, &tm);
+            si = it->second.Intersect(r, tm);
+            if (si) {
+                si->intr = (*tp->renderFromPrimitive)(si->intr);
+                si->intr.instanceId = tp->instanceId;
+            }
+        }
+        if (!si || si->tHit != h.t) ++nMismatch;
+        return si;
+    }
+
+    static void Pack(const Ray &r, Float tMax, float *q) {
+        q[0] = r.o.x; q[1] = r.o.y; q[2] = r.o.z;
+        q[3] = r.d.x; q[4] = r.d.y; q[5] = r.d.z;
+        q[6] = tMax;
+    }
+
+    void IntersectClosest(int maxRays, const RayQueue *rayQ, EscapedRayQueue *escapedRayQ,
+                          HitAreaLightQueue *hitAreaLightQ, MaterialEvalQueue *basicMtlQ,
+                          MaterialEvalQueue *universalMtlQ, MediumSampleQueue *mediumSampleQ,
+                          RayQueue *nextRayQ) const override {
+        const int n = rayQ->Size();
+        if (n == 0) return;
+        std::vector<float> rays(size_t(n) * 7);
+        ParallelFor(0, n, [&](int64_t i) { Pack((*rayQ)[i].ray, Infinity, &rays[size_t(i) * 7]); });
+        std::vector<b200pt_hit> hits(n);
+        check(b200pt_intersect_closest(scene, rays.data(), n, hits.data(), B200PT_MEM_HOST), ctx, "b200pt_intersect_closest");
+        nClosest += n;
+        ParallelFor(0, n, [&](int64_t i) {  // wavefront/aggregate.cpp:42-57, with the search done on the GPU
+            const RayWorkItem r = (*rayQ)[i];
+            pstd::optional<ShapeIntersection> si;
+            if (hits[i].mesh != 0xFFFFFFFFu) si = Rebuild(r.ray, Infinity, hits[i]);
+            if (!si)
+                EnqueueWorkAfterMiss(r, mediumSampleQ, escapedRayQ);
+            else
+                EnqueueWorkAfterIntersection(r, r.ray.medium, si->tHit, si->intr, mediumSampleQ, nextRayQ, hitAreaLightQ,
+                                             basicMtlQ, universalMtlQ);
+        });
+    }
+
+    void IntersectShadow(int maxRays, ShadowRayQueue *q, SOA<PixelSampleState> *pixelSampleState) const override {
+        const int n = q->Size();
+        if (n == 0) return;
+        std::vector<float> rays(size_t(n) * 7);
+        ParallelFor(0, n, [&](int64_t i) {
+            const ShadowRayWorkItem w = (*q)[i];
+            Pack(w.ray, w.tMax, &rays[size_t(i) * 7]);
+        });
+        std::vector<uint8_t> occ(n);
+        check(b200pt_intersect_any(scene, rays.data(), n, occ.data(), B200PT_MEM_HOST), ctx, "b200pt_intersect_any");
+        nShadow += n;
+        ParallelFor(0, n, [&](int64_t i) { RecordShadowRayResult((*q)[i], pixelSampleState, occ[i] != 0); });
+    }
+
+    // one ray through the GPU (the walks below are sequential per ray: segment k + 1 starts where segment k ended)
+    pstd::optional<ShapeIntersection> IntersectOne(const Ray &ray, Float tMax) const {
+        float q[7];
+        Pack(ray, tMax, q);
+        b200pt_hit h;
+        {
+            std::lock_guard<std::mutex> lock(mu);  // one context = one stream: calls are serialised
+            check(b200pt_intersect_closest(scene, q, 1, &h, B200PT_MEM_HOST), ctx, "b200pt_intersect_closest");
+        }
+        ++nSingle;
+        if (h.mesh == 0xFFFFFFFFu) return {};
+        return Rebuild(ray, tMax, h);
+    }
+
+    // wavefront/aggregate.cpp:72-90: TraceTransmittance (wavefront/intersect.h:164-274) with the reference's own
+    // ratio-tracking code and this aggregate as the intersector.  (The product's transmittance walks run inside
+    // b200pt_render_run; this adaptor is the test vehicle for the intersector plug.)
+    void IntersectShadowTr(int maxRays, ShadowRayQueue *q, SOA<PixelSampleState> *pixelSampleState) const override {
+        for (int index = 0; index < q->Size(); ++index) {
+            const ShadowRayWorkItem w = (*q)[index];
+            pstd::optional<ShapeIntersection> si;
+            TraceTransmittance(
+                w, pixelSampleState,
+                [&](Ray ray, Float tMax) -> TransmittanceTraceResult {
+                    si = IntersectOne(ray, tMax);
+                    if (!si) return TransmittanceTraceResult{false, Point3f(), pbrt::Material()};
+                    return TransmittanceTraceResult{true, si->intr.p(), si->intr.material};
+                },
+                [&](Point3f p) -> Ray { return si->intr.SpawnRayTo(p); });
+        }
+    }
+
+    // wavefront/aggregate.cpp:92-116
+    void IntersectOneRandom(int maxRays, SubsurfaceScatterQueue *subsurfaceScatterQueue) const override {
+        for (int index = 0; index < subsurfaceScatterQueue->Size(); ++index) {
+            const SubsurfaceScatterWorkItem &w = (*subsurfaceScatterQueue)[index];
+            uint64_t seed = Hash(w.p0, w.p1);
+            WeightedReservoirSampler<SubsurfaceInteraction> wrs(seed);
+            Interaction base(w.p0, 0.f, Medium());
+            while (true) {
+                Ray r = base.SpawnRayTo(w.p1);
+                if (r.d == Vector3f(0, 0, 0)) break;
+                pstd::optional<ShapeIntersection> si = IntersectOne(r, 1);
+                if (!si) break;
+                base = si->intr;
+                if (si->intr.material == w.material) wrs.Add(SubsurfaceInteraction(si->intr), 1.f);
+            }
+            if (wrs.HasSample()) {
+                subsurfaceScatterQueue->reservoirPDF[index] = wrs.SampleProbability();
+                subsurfaceScatterQueue->ssi[index] = wrs.GetSample();
+            } else
+                subsurfaceScatterQueue->reservoirPDF[index] = 0;
+        }
+    }
+
+  private:
+    Primitive aggregate;
+    b200pt_ctx *ctx = nullptr;
+    b200pt_scene *scene = nullptr;
+    size_t nTriMeshes = 0;
+    std::vector<uint32_t> refMesh;  // library mesh id -> reference mesh id (patch meshes after the triangle meshes)
+    std::unordered_map<uint64_t, Primitive> primOf;
+    std::vector<const TransformedPrimitive *> instances;
+    mutable std::mutex mu;
+    mutable std::atomic<uint64_t> nClosest{0}, nShadow{0}, nSingle{0}, nMismatch{0};
+};
+
+// RenderWavefront (wavefront/wavefront.cpp:14-70) with the aggregate the integrator constructed
+// (wavefront/integrator.cpp:157-169) replaced by B200Aggregate over the same host-built BVH.
+static void RenderWavefrontB200(BasicScene &scene, int device) {
+    WavefrontPathIntegrator *integrator = new WavefrontPathIntegrator(pstd::pmr::get_default_resource(), scene);
+    CPUAggregate *cpu = dynamic_cast<CPUAggregate *>(integrator->aggregate);
+    if (!cpu) die("the integrator's aggregate is not the CPUAggregate");
+    integrator->aggregate = new B200Aggregate(cpu->aggregate, device);
+    Float seconds = integrator->Render();
+    delete integrator->aggregate;
+    ImageMetadata metadata;
+    integrator->camera.InitMetadata(&metadata);
+    metadata.renderTimeSeconds = seconds;
+    metadata.samplesPerPixel = integrator->sampler.SamplesPerPixel();
+    integrator->film.WriteImage(metadata);
+}
+
+int main(int argc, char *argv[]) {
+    PBRTOptions options;
+    options.quiet = true;
+    std::vector<std::string> filenames;
+    bool wavefront = false, ownBvh = false;
+    int device = 0;
+    auto onError = [](const std::string &err) {
+        fprintf(stderr, "pbrt_b200: %s\n", err.c_str());
+        exit(1);
+    };
+    std::vector<std::string> args = GetCommandLineArguments(argv);
+    for (auto iter = args.begin(); iter != args.end(); ++iter) {
+        if ((*iter)[0] != '-') {
+            filenames.push_back(*iter);
+            continue;
+        }
+        if (ParseArg(&iter, args.end(), "nthreads", &options.nThreads, onError) ||
+            ParseArg(&iter, args.end(), "spp", &options.pixelSamples, onError) ||
+            ParseArg(&iter, args.end(), "seed", &options.seed, onError) ||
+            ParseArg(&iter, args.end(), "outfile", &options.imageFile, onError) ||
+            ParseArg(&iter, args.end(), "wavefront", &wavefront, onError) ||
+            ParseArg(&iter, args.end(), "own-bvh", &ownBvh, onError) ||  // let the library build the trees itself
+            ParseArg(&iter, args.end(), "device", &device, onError))
+            continue;
+        onError("unknown option " + *iter);
+    }
+    if (filenames.empty()) onError("usage: pbrt_b200 [--wavefront] [--spp n] [--nthreads n] [--outfile f] scene.pbrt");
+    options.wavefront = wavefront;
+    InitPBRT(options);
+    {
+        BasicScene scene;
+        BasicSceneBuilder builder(&scene);
+        ParseFiles(&builder, filenames);
+        if (wavefront) RenderWavefrontB200(scene, device);  // cmd/pbrt.cpp:296-299
+        else RenderB200(scene, device, !ownBvh);
+    }
+    fflush(stdout);
+    fflush(stderr);
+    _Exit(0);
+}

@@ -66,7 +66,7 @@ LIB := $(OUT)/libpbrt_ref.a
 # dumps, never EXR; calling it would fault.
 LDFLAGS := -pthread -no-pie -Wl,--unresolved-symbols=ignore-all
 
-all: $(OUT)/pbrt_ref $(OUT)/raycast_ref $(OUT)/dumpscene_ref
+all: $(OUT)/pbrt_ref $(OUT)/raycast_ref $(OUT)/dumpscene_ref $(OUT)/pbrt_b200
 
 $(GEN)/soac: $(REF)/src/pbrt/cmd/soac.cpp
 	@mkdir -p $(GEN)
@@ -135,7 +135,12 @@ $(OUT)/pbrt_ref: $(REF)/src/pbrt/cmd/pbrt.cpp $(LIB)
 # unchanged so it links against the normally-compiled library.
 $(OUT)/raycast_ref: oracle/raycast_ref.cpp $(LIB)
 	$(CXX) $(CXXFLAGS) $< $(LIB) $(LDFLAGS) -o $@
-$(OUT)/dumpscene_ref: oracle/dumpscene_ref.cpp $(LIB)
+$(OUT)/dumpscene_ref: oracle/dumpscene_ref.cpp oracle/flatten_ref.h $(LIB)
 	$(CXX) $(CXXFLAGS) $< $(LIB) $(LDFLAGS) -o $@
+# The reference-side binding, compiled: the reference's parser / scene objects / film writer with
+# the product's shared library behind them (Level 2 RenderB200, Level 1 B200Aggregate : WavefrontAggregate).
+B200LIB ?= pbrt-v4_b200/libb200pt.so
+$(OUT)/pbrt_b200: oracle/pbrt_b200.cpp oracle/flatten_ref.h include/b200pt.h $(LIB) $(B200LIB)
+	$(CXX) $(CXXFLAGS) $< $(LIB) -L$(dir $(B200LIB)) -lb200pt $(LDFLAGS) '-Wl,-rpath,$$ORIGIN/../../pbrt-v4_b200' -o $@
 
 .PHONY: all

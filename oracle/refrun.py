@@ -101,6 +101,36 @@ def render(pbrt_file, out_pfm, nthreads=None, timeout=3600):
     return read_pfm(out_pfm), dt
 
 
+PBRT_B200 = os.path.join(REF_DIR, "pbrt_b200")
+
+
+def b200_available():
+    return os.access(PBRT_B200, os.X_OK)
+
+
+def render_b200(pbrt_file, out_pfm, wavefront=False, extra=(), timeout=3600):
+    """The compiled reference-side binding (oracle/pbrt_b200.cpp): the reference's parser, scene objects and film
+    writer with libb200pt.so behind them.  wavefront=True: the reference's own WavefrontPathIntegrator over
+    B200Aggregate.  Returns (image, seconds, stderr)."""
+    import time
+    args = [PBRT_B200] + (["--wavefront"] if wavefront else []) + list(extra) + [pbrt_file]
+    t = time.time()
+    r = subprocess.run(args, capture_output=True, text=True, timeout=timeout, cwd=os.path.dirname(pbrt_file))
+    dt = time.time() - t
+    if r.returncode != 0:
+        raise RuntimeError(f"pbrt_b200 failed ({r.returncode}): {r.stderr[-2000:]}")
+    return read_pfm(out_pfm), dt, r.stderr
+
+
+def render_wavefront(pbrt_file, out_pfm, nthreads=None, timeout=3600):
+    """pbrt_ref --wavefront: the reference's CPU wavefront path (CPUAggregate)."""
+    args = [PBRT, "--quiet", "--wavefront"] + (["--nthreads", str(nthreads)] if nthreads else []) + [pbrt_file]
+    r = subprocess.run(args, capture_output=True, text=True, timeout=timeout, cwd=os.path.dirname(pbrt_file))
+    if r.returncode != 0:
+        raise RuntimeError(f"pbrt_ref --wavefront failed ({r.returncode}): {r.stderr[-2000:]}")
+    return read_pfm(out_pfm)
+
+
 def dump_scene(pbrt_file, out_b2rs, bvh=True):
     """Scene tables as the reference's own parser + object creation produced them (dumpscene_ref.cpp).
     bvh=False leaves the reference's BVH node arrays out of the file."""
