@@ -176,6 +176,18 @@ int b200pt_intersect_any(b200pt_scene *scene, const float *rays, int64_t n,
                          uint8_t *occluded, uint32_t mem);
 int b200pt_get_trace_stats(const b200pt_scene *scene, b200pt_trace_stats *out);
 
+/* b200pt_intersect_closest for callers that may not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernel and same results as b200pt_intersect_closest with B200PT_MEM_DEVICE (rays_dev / hits_dev are device
+ * buffers of the caller; asynchronous on the context's stream), but the kernel's scratch (ray-fetch counter + the list
+ * of rays handed to the exact walk) is a static __device__ array of 4 * (65 + B200PT_NOALLOC_MAX_RAYS) bytes (~4 MB)
+ * that every GPU loading the library holds until exit, and the call makes no cudaMalloc / cudaFree.
+ * n > B200PT_NOALLOC_MAX_RAYS -> B200PT_ERR_INVALID (message in b200pt_last_error).  All calls on one device share the
+ * array: calls that overlap on the GPU (other streams or contexts of the same device) race; calls queued on one
+ * stream do not.  Trace counters / kernel_ms are not recorded for these calls. */
+#define B200PT_NOALLOC_MAX_RAYS (1 << 20)
+int b200pt_intersect_closest_noalloc(b200pt_scene *scene, const float *rays_dev, int64_t n, b200pt_hit *hits_dev);
+
 /* ------------------------------------------------------------------ render path
  * b200pt_render_create replaces the object construction of RenderWavefront / the
  * WavefrontPathIntegrator constructor (wavefront/wavefront.cpp:14-70, wavefront/integrator.cpp:89-199):

@@ -24,6 +24,7 @@ CU_SOURCES = [
     ("traverse_bvh2.cu", ["--fmad=false"]),
     ("traverse_persist.cu", ["--fmad=false"]),
     ("render.cu", ["--fmad=false"]),
+    ("noalloc.cu", []),
 ]
 
 

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "libb200pt.so")
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_NOMEM = 0, 1, 2, 3, 4
 MEM_HOST, MEM_DEVICE = 0, 1
 TRACE_COUNTERS = 1 << 8
+NOALLOC_MAX_RAYS = 1 << 20  # B200PT_NOALLOC_MAX_RAYS
 MISS = 0xFFFFFFFF
 
 HIT_DTYPE = np.dtype([("mesh", "<u4"), ("prim", "<u4"), ("instance", "<u4"),
@@ -78,6 +79,7 @@ SYMBOLS = {
     "b200pt_scene_get_stats": (C.c_int, [C.c_void_p, C.POINTER(SceneStats)]),
     "b200pt_intersect_closest": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint32]),
     "b200pt_intersect_any": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint32]),
+    "b200pt_intersect_closest_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "b200pt_get_trace_stats": (C.c_int, [C.c_void_p, C.POINTER(TraceStats)]),
     "b200pt_bvh2_build": (C.c_int, [C.POINTER(C.c_float), C.c_uint32, C.c_int, C.c_void_p,
                                     C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
