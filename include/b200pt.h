@@ -146,6 +146,9 @@ typedef struct b200pt_trace_stats {
      * the exact binary kernel instead (non-finite 1/d or origin, at the top level or inside an instance) */
     uint64_t wide_nodes_visited;
     uint64_t exact_rays;
+    /* leaves whose own box got the reference's exact test in the 8-wide walk (32 B each; the wide nodes' own eight
+     * tests are a conservative filter, csrc/wide.h) */
+    uint64_t leaf_boxes_tested;
 } b200pt_trace_stats;
 
 enum { B200PT_TRACE_COUNTERS = 1u << 8 };

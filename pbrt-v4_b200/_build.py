@@ -22,7 +22,13 @@ CPP_SOURCES = ["bvh2_build.cpp", "wide_build.cpp", "scene_host.cpp", "render_hos
 # (file, extra nvcc flags)
 CU_SOURCES = [
     ("traverse_bvh2.cu", ["--fmad=false"]),
-    ("traverse_persist.cu", ["--fmad=false"]),
+    # one family of kernels per part (see the end of traverse_persist.cu), built in parallel
+    ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=0"], "traverse_persist_0"),
+    ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=1"], "traverse_persist_1"),
+    ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=2"], "traverse_persist_2"),
+    ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=3"], "traverse_persist_3"),
+    ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=4"], "traverse_persist_4"),
+    ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=5"], "traverse_persist_5"),
     ("render.cu", ["--fmad=false"]),
     ("noalloc.cu", []),
 ]
@@ -47,23 +53,28 @@ def _run(cmd, verbose):
 
 
 def build(verbose=False, force=False):
+    from concurrent.futures import ThreadPoolExecutor
     os.makedirs(OBJ, exist_ok=True)
-    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".h")]
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".h") or f.endswith(".cuh")]
     headers.append(os.path.join(os.path.dirname(HERE), "include", "b200pt.h"))
-    objs = []
+    objs, jobs = [], []
     for f in CPP_SOURCES:
         src, obj = os.path.join(CSRC, f), os.path.join(OBJ, f + ".o")
         objs.append(obj)
         if force or _newer(src, obj, headers):
-            _run(["g++", "-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-fno-fast-math",
-                  "-march=x86-64-v3", "-Wall", "-I" + os.path.join(CUDA_HOME, "include"),
-                  "-c", src, "-o", obj], verbose)
-    for f, extra in CU_SOURCES:
-        src, obj = os.path.join(CSRC, f), os.path.join(OBJ, f + ".o")
+            jobs.append(["g++", "-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-fno-fast-math",
+                         "-march=x86-64-v3", "-Wall", "-I" + os.path.join(CUDA_HOME, "include"),
+                         "-c", src, "-o", obj])
+    for entry in CU_SOURCES:
+        f, extra = entry[0], entry[1]
+        src, obj = os.path.join(CSRC, f), os.path.join(OBJ, (entry[2] if len(entry) > 2 else f) + ".o")
         objs.append(obj)
         if force or _newer(src, obj, headers):
-            _run([NVCC, "-std=c++17", "-O3", "-lineinfo", "-Xptxas", "-v", "-Xcompiler", "-fPIC",
-                  "-Xcompiler", "-ffp-contract=off"] + GENCODE + extra + os.environ.get("B200PT_NVCC_EXTRA", "").split() + ["-c", src, "-o", obj], verbose)
+            jobs.append([NVCC, "-std=c++17", "-O3", "-lineinfo", "-Xptxas", "-v", "-Xcompiler", "-fPIC",
+                         "-Xcompiler", "-ffp-contract=off"] + GENCODE + extra + os.environ.get("B200PT_NVCC_EXTRA", "").split() + ["-c", src, "-o", obj])
+    if jobs:
+        with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
+            list(ex.map(lambda c: _run(c, verbose), jobs))
     if force or any(_newer(o, LIB, []) for o in objs):
         _run([NVCC, "-shared", "-o", LIB] + objs + GENCODE + ["-cudart", "static"], verbose)
     return LIB

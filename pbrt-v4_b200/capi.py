@@ -61,7 +61,7 @@ class SceneStats(C.Structure):
 class TraceStats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("leaves_visited", C.c_uint64),
                 ("prims_tested", C.c_uint64), ("kernel_ms", C.c_float), ("wide_nodes_visited", C.c_uint64),
-                ("exact_rays", C.c_uint64)]
+                ("exact_rays", C.c_uint64), ("leaf_boxes_tested", C.c_uint64)]
 
 
 # every symbol include/b200pt.h declares: name -> (restype, argtypes)

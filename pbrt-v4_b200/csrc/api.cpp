@@ -97,7 +97,7 @@ int b200pt_context_create(int device, b200pt_ctx **out) {
     c->simpleKernel = mode && std::string(mode) == "simple";
     c->wideKernel = !(mode && (std::string(mode) == "binary" || std::string(mode) == "pair"));
     if (const char *v = getenv("B200PT_REFILL_MIN")) c->refillMin = std::max(1, std::min(32, atoi(v)));
-    if (const char *v = getenv("B200PT_NODE_MIN")) c->nodeMin = std::max(1, std::min(32, atoi(v)));
+    if (const char *v = getenv("B200PT_NODE_MIN")) c->nodeMin = std::max(0, std::min(32, atoi(v)));
     *out = c;
     return B200PT_OK;
 }
@@ -169,6 +169,10 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     if (e == cudaSuccess && wideBytes) e = cudaMalloc(&s->dWide, wideBytes);
     if (e == cudaSuccess && wideBytes)
         e = cudaMemcpyAsync(s->dWide, h.wide.data(), wideBytes, cudaMemcpyHostToDevice, ctx->stream);
+    size_t leafBytes = h.leafBoxes.size() * sizeof(LeafBox);
+    if (e == cudaSuccess && leafBytes) e = cudaMalloc(&s->dLeafBoxes, leafBytes);
+    if (e == cudaSuccess && leafBytes)
+        e = cudaMemcpyAsync(s->dLeafBoxes, h.leafBoxes.data(), leafBytes, cudaMemcpyHostToDevice, ctx->stream);
     size_t instBytes = h.instances.size() * sizeof(InstanceDev);
     if (e == cudaSuccess && instBytes) e = cudaMalloc(&s->dInst, instBytes);
     if (e == cudaSuccess && instBytes)
@@ -186,6 +190,7 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     s->dev.rootRef = h.rootRef;
     s->dev.wide = s->dWide;  // null when every tree is a single leaf: the binary kernel handles that
     s->dev.rootWide = h.rootWide;
+    s->dev.leafBoxes = s->dLeafBoxes;
     s->dev.maxStackWide = h.maxStackWide;
     s->dev.instances = (const InstanceDev *)s->dInst;
     s->dev.rootNode = h.rootNode;
@@ -198,7 +203,7 @@ int b200pt_scene_create(b200pt_ctx *ctx, const b200pt_scene_desc *desc, b200pt_s
     s->stats.n_instances = h.instances.size();
     s->stats.n_bvh2_nodes = h.nodes.size();
     s->stats.n_wide_nodes = h.wide.size();
-    s->stats.device_bytes = nodeBytes + primBytes + pairBytes + instBytes + wideBytes;
+    s->stats.device_bytes = nodeBytes + primBytes + pairBytes + instBytes + wideBytes + leafBytes;
     s->stats.build_seconds = h.buildSeconds;
     s->stats.upload_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     *out = s;
@@ -213,6 +218,7 @@ int b200pt_scene_destroy(b200pt_scene *s) {
     if (s->dPrims) cudaFree(s->dPrims);
     if (s->dPairs) cudaFree(s->dPairs);
     if (s->dWide) cudaFree(s->dWide);
+    if (s->dLeafBoxes) cudaFree(s->dLeafBoxes);
     if (s->dInst) cudaFree(s->dInst);
     delete s;
     return B200PT_OK;
@@ -352,6 +358,7 @@ static int Intersect(b200pt_scene *s, const float *rays, int64_t n, void *out, u
         s->trace.leaves_visited = c[1];
         s->trace.prims_tested = c[2];
         s->trace.wide_nodes_visited = c[3];
+        s->trace.leaf_boxes_tested = c[4];
         if (exact) {
             int nExact = 0;
             B2_CUDA(ctx, cudaMemcpyAsync(&nExact, exact, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));

@@ -43,7 +43,7 @@ struct b200pt_scene {
     b200pt_ctx *ctx = nullptr;
     b200pt::HostScene host;
     b200pt::DeviceScene dev{};
-    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr, *dPairs = nullptr, *dWide = nullptr;
+    void *dNodes = nullptr, *dPrims = nullptr, *dInst = nullptr, *dPairs = nullptr, *dWide = nullptr, *dLeafBoxes = nullptr;
     b200pt_scene_stats stats{};
     b200pt_trace_stats trace{};
 };

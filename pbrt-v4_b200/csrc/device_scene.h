@@ -51,7 +51,7 @@ struct alignas(16) InstanceDev {
     uint32_t instanceId; // 1-based (scene.cpp:1560)
     uint32_t rootNode;   // the same root in `nodes` (Node32 layout)
     uint32_t object;
-    int32_t rootWide;    // the object's root in the wide layout: Wide8 index, or ~slot
+    int32_t rootWide;    // the object's root in the wide layout: Wide8 index, or ~(LeafBox index)
     uint32_t pad;
 };
 static_assert(sizeof(InstanceDev) == 176, "InstanceDev layout");
@@ -69,8 +69,9 @@ struct DeviceScene {
     uint32_t nInstances;
     uint32_t maxDepth;   // deepest root-to-leaf path over all trees (stack entries needed)
     const void *wide;    // Wide8[] (wide.h), or null: the scene is traversed by the binary kernel only
-    int32_t rootWide;    // Wide8 index of the top-level root, or ~slot
+    int32_t rootWide;    // Wide8 index of the top-level root, or ~(LeafBox index)
     uint32_t maxStackWide;
+    const void *leafBoxes; // LeafBox[] (wide.h): the leaves of the wide layout
     uint32_t hasPatches; // some PrimSlot is a bilinear patch (the kernels then read the slots' last 16 bytes)
 };
 

@@ -155,6 +155,52 @@ B2_HD bool SlabPlanesRegular(const RayCtx &r, float nx, float ny, float nz, floa
     return (tMin <= tMax) & (tMax > 0);
 }
 
+// CONSERVATIVE slab test of the wide walk (wide.h): one fma per plane.
+//   The reference's near product of plane b along axis k is fl(fl(b - o) * i) (i = 1/d), its far product that times
+//   (1 + 2 gamma_3), one more rounding.  With |b| <= B (the tree's root box holds every box under it) and
+//   M = B + |o|: |b - o| <= M, so each product lies within  M |i| (2^-23 + 2^-22 * 1.5 + 2^-24) < 2.25 * 2^-22 M |i|  of
+//   the exact (b - o) i.  Here the plane's value is fma(b, i, c) with c = -fl(o i) -+ e, e = M |i| 2^-19: the three
+//   roundings (o i, the sum c, the fma) cost at most 3 * 2^-24 (1 + 2^-18) M |i|, so the near value is BELOW the
+//   reference's near product and the far value ABOVE its padded far product, with a margin of more than 2^-20 M |i|.
+//   Hence  max(near values, 0) <= min(far values, tMaxS)  holds whenever the reference's test passes with any
+//   raytMax <= tMaxS (its conditions are tMin <= tMax, tMax > 0, tMin < raytMax on the bracketed quantities).
+// The ray must be regular: 1/d finite and non-zero, o and the bounds finite (else 0 * inf = NaN), M |i| a normal number
+// on every axis; WideRaySetup says so.
+struct WideRay {
+    float cNx, cNy, cNz;  // near planes: fma(b, i, cN)
+    float cFx, cFy, cFz;  // far planes:  fma(b, i, cF)
+};
+
+B2_HD bool WideRaySetup(const RayCtx &r, const float *treeBox, WideRay &w) {
+    const float Mx = B2_ADD(fmaxf(fabsf(treeBox[0]), fabsf(treeBox[3])), fabsf(r.ox));
+    const float My = B2_ADD(fmaxf(fabsf(treeBox[1]), fabsf(treeBox[4])), fabsf(r.oy));
+    const float Mz = B2_ADD(fmaxf(fabsf(treeBox[2]), fabsf(treeBox[5])), fabsf(r.oz));
+    // M |i| per axis; below 2^-100 the products are denormal and their roundings no longer relative: exact walk
+    const float mx = B2_MUL(Mx, fabsf(r.ix)), my = B2_MUL(My, fabsf(r.iy)), mz = B2_MUL(Mz, fabsf(r.iz));
+    const float ex = B2_MUL(mx, 0x1p-19f), ey = B2_MUL(my, 0x1p-19f), ez = B2_MUL(mz, 0x1p-19f);
+    const float oix = B2_MUL(r.ox, r.ix), oiy = B2_MUL(r.oy, r.iy), oiz = B2_MUL(r.oz, r.iz);
+    w.cNx = B2_SUB(-oix, ex);
+    w.cNy = B2_SUB(-oiy, ey);
+    w.cNz = B2_SUB(-oiz, ez);
+    w.cFx = B2_ADD(-oix, ex);
+    w.cFy = B2_ADD(-oiy, ey);
+    w.cFz = B2_ADD(-oiz, ez);
+    // every magnitude finite (a NaN or an infinity anywhere makes the sum non-finite; so does an overflow of finite
+    // terms: that ray merely takes the exact walk too); |o i| <= M |i|, so the three M |i| bound everything above
+    const float mag = B2_ADD(B2_ADD(mx, my), mz);
+    return (mag < INFINITY) & (fminf(fminf(mx, my), mz) > 0x1p-100f);
+}
+
+// near / far planes picked as the reference picks them (near = dirIsNeg ? pMax : pMin).  tNearOut <= the reference's
+// tMin of this box.  An empty slot's box (+inf, -inf) gives near = +inf, far = -inf: rejected, no NaN.
+B2_HD bool WideChildTest(const RayCtx &r, const WideRay &w, float nx, float ny, float nz, float fx, float fy, float fz,
+                         float tMaxS, float &tNearOut) {
+    const float tNear = fmaxf(fmaxf(B2_FMA(nx, r.ix, w.cNx), B2_FMA(ny, r.iy, w.cNy)), B2_FMA(nz, r.iz, w.cNz));
+    const float tFar = fminf(fminf(B2_FMA(fx, r.ix, w.cFx), B2_FMA(fy, r.iy, w.cFy)), B2_FMA(fz, r.iz, w.cFz));
+    tNearOut = tNear;
+    return fmaxf(tNear, 0.f) <= fminf(tFar, tMaxS);
+}
+
 B2_HD bool SlabTest(const RayCtx &r, const float *bmin, const float *bmax, float raytMax) {
     float tMin;
     return SlabCore(r, bmin, bmax, tMin) & (tMin < raytMax);

@@ -351,12 +351,13 @@ int AssembleScene(const b200pt_scene_desc *desc, HostScene &out, std::string &er
     }
     // ---- the 8-wide collapse of every tree
     out.wide.clear();
+    out.leafBoxes.clear();
     out.treeRootWide.clear();
     {
         uint32_t topStack = 1, objStack = 0;
         for (size_t ti = 0; ti < out.trees.size(); ++ti) {
             uint32_t st = 1;
-            out.treeRootWide.push_back(BuildWide(out.nodes, out.treeRoot[ti], out.wide, &st));
+            out.treeRootWide.push_back(BuildWide(out.nodes, out.treeRoot[ti], out.wide, out.leafBoxes, &st));
             if (ti == 0) topStack = st;
             else objStack = std::max(objStack, st);
         }

@@ -28,7 +28,8 @@ struct HostScene {
     std::vector<int32_t> treeRootRef; // per tree: PairNode index or ~slot
     int32_t rootRef = 0;
     std::vector<Wide8> wide;         // 8-wide collapse of the same trees (traverse_wide.cu)
-    std::vector<int32_t> treeRootWide; // per tree: Wide8 index or ~slot
+    std::vector<LeafBox> leafBoxes;  // the leaves as the wide walk enters them (wide.h)
+    std::vector<int32_t> treeRootWide; // per tree: Wide8 index or ~(LeafBox index)
     int32_t rootWide = 0;
     uint32_t maxStackWide = 1;       // stack entries the wide traversal can need (top level + deepest object)
     std::vector<InstanceDev> instances;

@@ -37,9 +37,19 @@ void VisitOrder(const std::vector<Node32> &nodes, uint32_t n, const uint32_t *cu
 
 }  // namespace
 
-int32_t BuildWide(const std::vector<Node32> &nodes, uint32_t root, std::vector<Wide8> &out, uint32_t *maxStackOut) {
+int32_t BuildWide(const std::vector<Node32> &nodes, uint32_t root, std::vector<Wide8> &out, std::vector<LeafBox> &leaves,
+                  uint32_t *maxStackOut) {
     if (maxStackOut) *maxStackOut = 1;
-    if (nodes[root].nPrims > 0) return ~nodes[root].offset;
+    auto addLeaf = [&](const Node32 &nd, uint32_t flag) {
+        LeafBox lb;
+        std::memcpy(lb.box, nd.bmin, 12);
+        std::memcpy(lb.box + 3, nd.bmax, 12);
+        lb.first = nd.offset;
+        lb.count = uint32_t(nd.nPrims) | flag;
+        leaves.push_back(lb);
+        return ~int32_t(leaves.size() - 1);
+    };
+    if (nodes[root].nPrims > 0) return addLeaf(nodes[root], kLeafNoTest);
     // extent of the tree in the depth-first array: up to the last node of the root's second subtree
     uint32_t last = root;
     while (nodes[last].nPrims == 0) last = uint32_t(nodes[last].offset);
@@ -153,7 +163,7 @@ int32_t BuildWide(const std::vector<Node32> &nodes, uint32_t root, std::vector<W
                 w.plane[3 + a][i] = c.bmax[a];
             }
             if (c.nPrims > 0) {
-                w.ref[i] = ~c.offset;
+                w.ref[i] = addLeaf(c, 0u);
             } else {
                 w.ref[i] = int32_t(out.size());
                 out.emplace_back();

@@ -553,14 +553,84 @@ CONFIG3_MATERIALS = ["dielectric_smooth", "conductor_rough", "coated_diffuse", N
                      "conductor_smooth", "coated_diffuse_rough", "conductor_reflectance"]
 
 
+def write_ply(path, mesh):
+    """Binary little-endian PLY of a triangle mesh (float32 x y z; uchar-counted int32 faces), as pbrt's
+    `Shape "plymesh"` reads it (util/mesh.cpp TriQuadMesh::ReadPLY)."""
+    p = np.ascontiguousarray(mesh.p, dtype="<f4")
+    idx = np.ascontiguousarray(mesh.indices, dtype="<i4").reshape(-1, 3)
+    face = np.empty(len(idx), dtype=[("n", "u1"), ("i", "<i4", 3)])
+    face["n"], face["i"] = 3, idx
+    with open(path, "wb") as f:
+        f.write((f"ply\nformat binary_little_endian 1.0\nelement vertex {len(p)}\nproperty float x\nproperty float y\n"
+                 f"property float z\nelement face {len(idx)}\nproperty list uchar int vertex_indices\nend_header\n").encode())
+        f.write(p.tobytes())
+        f.write(face.tobytes())
+
+
+def config3_object_meshes(n_objects, n_instances, grid):
+    """The object definitions of config3_pbrt(n_objects, grid, n_instances, ...), in object space: the generator's
+    random stream does not depend on `grid`, so the same shapes come out at any tessellation."""
+    rng = np.random.default_rng(3000 + n_objects * 7 + n_instances)
+    out = []
+    for _ in range(n_objects):
+        rng.uniform(0.2, 0.8, 3)  # the object's diffuse colour
+        out.append(_bumpy_torus(rng, grid, grid))
+    return out
+
+
+def config3_refine(d, n_objects, n_instances, grid):
+    """Scene tables `d` dumped from config3_pbrt at a coarse tessellation -> the same scene with every object
+    definition tessellated at `grid` (2 * grid^2 triangles each): BASELINE configs[2] at its full size of unique
+    triangles without a dump of that size in the repository.  The dump holds an object's vertices in the render
+    space of its definition, object space plus one translation, which is read off the coarse meshes and checked."""
+    nv, nt = d["mesh_nverts"].astype(np.int64), d["mesh_ntris"].astype(np.int64)
+    vo, to = np.concatenate([[0], np.cumsum(nv)]), np.concatenate([[0], np.cumsum(nt)])
+    obj = d["mesh_object"]
+    coarse_grid = int(round(np.sqrt(nt[obj >= 0][0] / 2)))
+    coarse = config3_object_meshes(n_objects, n_instances, coarse_grid)
+    fine = config3_object_meshes(n_objects, n_instances, grid)
+    P, I, nv2, nt2 = [], [], nv.copy(), nt.copy()
+    shift = None
+    # the host numbers the definitions in its own (hash map) order; instance i places "obj{i % n_objects}"
+    assert n_instances >= n_objects
+    index_of = {int(d["instance_object"][i]): i for i in range(n_objects)}
+    for m in range(len(nv)):
+        if obj[m] < 0:
+            P.append(d["P"][vo[m]:vo[m + 1]])
+            I.append(d["indices"][to[m]:to[m + 1]])
+            continue
+        c, f = coarse[index_of[int(obj[m])]], fine[index_of[int(obj[m])]]
+        dumped = d["P"][vo[m]:vo[m + 1]]
+        if shift is None:
+            shift = (dumped[0].astype(np.float64) - c.p[0].astype(np.float64)).astype(np.float32)
+        # the reference applies render-from-object as x * 1 + t in float: one rounding
+        assert np.array_equal(dumped, c.p + shift) and np.array_equal(d["indices"][to[m]:to[m + 1]], c.indices), \
+            "the dump is not config3_pbrt's scene at a coarser tessellation"
+        P.append(f.p + shift)
+        I.append(f.indices)
+        nv2[m], nt2[m] = len(f.p), len(f.indices)
+    out = dict(d)
+    out["P"] = np.ascontiguousarray(np.concatenate(P), np.float32)
+    out["indices"] = np.ascontiguousarray(np.concatenate(I), np.int32)
+    out["mesh_nverts"], out["mesh_ntris"] = nv2.astype(d["mesh_nverts"].dtype), nt2.astype(d["mesh_ntris"].dtype)
+    return out
+
+
 def config3_pbrt(path, n_objects=32, grid=32, n_instances=4883, n_lights=1024, res=(1920, 1080), spp=1024,
-                 maxdepth=5, out="config3.pfm", seed=0, crop=None):
+                 maxdepth=5, out="config3.pfm", seed=0, crop=None, scale=(0.8, 2.2), ply_dir=None):
     """BASELINE configs[2]: procedural instanced scene (n_instances x 2 * grid^2 triangles ~ 10 M at the
     defaults) of dielectric / conductor / coated / diffuse objects over a ground plane, lit by n_lights
     small emissive quads (2 triangles each) through the light-BVH sampler, plus a dim uniform sky.
     Every object definition carries one material; instances are rotation x uniform scale x translation.
     crop = (x0, x1, y0, y1) in NDC renders a window of the frame (for the bounded CPU baseline)."""
     rng = np.random.default_rng(3000 + n_objects * 7 + n_instances)
+
+    def shape(o, mesh):  # inline, or a binary PLY next to the scene file (ply_dir: full-size meshes)
+        if ply_dir is None:
+            return _mesh_pbrt(mesh)
+        write_ply(os.path.join(ply_dir, f"obj{o}.ply"), mesh)
+        return f'Shape "plymesh" "string filename" "{os.path.join(ply_dir, f"obj{o}.ply")}"'
+
     lines = [
         'LookAt 0 14 -48  0 3 0  0 1 0',
         'Camera "perspective" "float fov" 38',
@@ -579,14 +649,14 @@ def config3_pbrt(path, n_objects=32, grid=32, n_instances=4883, n_lights=1024, r
         c = rng.uniform(0.2, 0.8, 3)
         lines += ['AttributeBegin',
                   '  ' + (MATERIALS[mat] if mat else f'Material "diffuse" "rgb reflectance" [{c[0]:.3f} {c[1]:.3f} {c[2]:.3f}]'),
-                  f'  ObjectBegin "obj{o}"', '    ' + _mesh_pbrt(_bumpy_torus(rng, grid, grid)), '  ObjectEnd', 'AttributeEnd']
+                  f'  ObjectBegin "obj{o}"', '    ' + shape(o, _bumpy_torus(rng, grid, grid)), '  ObjectEnd', 'AttributeEnd']
     for i in range(n_instances):
         t = (rng.uniform(-30, 30), rng.uniform(0.6, 9.0), rng.uniform(-30, 30))
         axis = rng.normal(size=3)
         axis /= np.linalg.norm(axis)
         lines += ['AttributeBegin', f'  Translate {t[0]:.5f} {t[1]:.5f} {t[2]:.5f}',
                   f'  Rotate {rng.uniform(0, 360):.4f} {axis[0]:.5f} {axis[1]:.5f} {axis[2]:.5f}',
-                  f'  Scale {rng.uniform(0.8, 2.2):.5f} ' * 1, ]
+                  f'  Scale {rng.uniform(scale[0], scale[1]):.5f} ' * 1, ]
         sc = lines.pop().split()[1]
         lines += [f'  Scale {sc} {sc} {sc}', f'  ObjectInstance "obj{i % n_objects}"', 'AttributeEnd']
     palette = [rng.uniform(20.0, 200.0) * rng.uniform(0.3, 1.0, 3) for _ in range(32)]  # 32 emission spectra

@@ -129,7 +129,7 @@ int main(int argc, char **argv) {
         bool h = false;
         int hw = -1;
         if (wideMode) {
-            hw = TraceWide(hs, hs.rootWide, hs.bounds, q, q + 3, tMax, any, best, -1);
+            hw = TraceWide(hs, hs.rootWide, hs.bounds, hs.bounds, q, q + 3, tMax, any, best, -1);
             if (hw < 0) {  // irregular ray: the exact binary walk, from scratch
                 ++nIrregular;
                 tMax = q[6];
@@ -152,9 +152,9 @@ int main(int argc, char **argv) {
     if (wideMode) {
         const WideCounters &c = WideStats();
         fprintf(stderr, "irregular rays: %zu of %zu; wide nodes %zu, max stack %u; per ray: %.2f wide visits (%.2f of 8 slots used, "
-                "%.2f children entered), %.2f leaves, %.2f prims\n", nIrregular, n, hs.wide.size(), hs.maxStackWide,
+                "%.2f children entered), %.2f leaf boxes tested, %.2f leaves, %.2f prims\n", nIrregular, n, hs.wide.size(), hs.maxStackWide,
                 double(c.visits) / n, c.visits ? double(c.children) / c.visits : 0., c.visits ? double(c.childHits) / c.visits : 0.,
-                double(c.leaves) / n, double(c.prims) / n);
+                double(c.leafTests) / n, double(c.leaves) / n, double(c.prims) / n);
     }
     return 0;
 }

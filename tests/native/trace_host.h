@@ -85,43 +85,59 @@ inline bool TracePairs(const HostScene &hs, int rootRef, const float *rootBox, c
     return any ? false : best.slot >= 0;
 }
 
-// Wide8 walk as traverse_wide.cu does it: every child box of the wide node gets the reference's slab test
-// (tMax-independent part, plus `tMin < tMax * (1 + 2^-10)`), the passing children are stacked by their rank in
-// the reference's visit order for the ray's octant (pre-set popcount; reversed when dirIsNeg[2]), and
-// `tMin < tMax` is decided at pop time.  Rays with a non-finite 1/d or origin go through TracePairs (`irregular`).
+// Wide8 walk as traverse_persist.cu (WIDE) does it: every child box of the wide node gets the CONSERVATIVE test
+// (isect.h WideChildTest, against tMax * (1 + 2^-10)), the passing children are stacked by their rank in the
+// reference's visit order for the ray's octant (pre-set popcount; reversed when dirIsNeg[2]), stale entries are
+// dropped at pop time, and a leaf is entered when its own box (LeafBox) passes the reference's exact test with the
+// tMax of that moment.  Rays that are not regular (WideRaySetup) go through TracePairs (`irregular`).
 struct WideCounters {
-    unsigned long long visits = 0, childHits = 0, leaves = 0, prims = 0, children = 0;
+    unsigned long long visits = 0, childHits = 0, leaves = 0, prims = 0, children = 0, leafTests = 0;
 };
 inline WideCounters &WideStats() {
     static WideCounters c;
     return c;
 }
 
-inline bool RayIsRegular(const RayCtx &r) {
-    return std::isfinite(r.ix) && std::isfinite(r.iy) && std::isfinite(r.iz) && std::isfinite(r.ox) &&
-           std::isfinite(r.oy) && std::isfinite(r.oz);
-}
-
 // returns 0 = no hit, 1 = hit, -1 = the ray (or its image inside an instance) is irregular: redo with TracePairs
-inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, const float *o, const float *d,
-                     float &tMax, bool any, Best &best, int curInst) {
+inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, const float *treeBox, const float *o,
+                     const float *d, float &tMax, bool any, Best &best, int curInst) {
     RayCtx r;
     RaySetup(r, o[0], o[1], o[2], d[0], d[1], d[2]);
-    if (!RayIsRegular(r)) return -1;
+    WideRay wr;
+    if (!WideRaySetup(r, treeBox, wr)) return -1;
     struct E { int ref; float t; };
     std::vector<E> stack(hs.maxStackWide + 8);
-    int sp = 0, cur = 0;
+    int sp = 0, cur = 0, lslot = 0, lcnt = 0;
     bool done = false;
+    // cur >= 0: wide node; cur < 0: leaf entered (lslot, lcnt set)
+    auto enterLeaf = [&](int ref) {
+        const LeafBox &lb = hs.leafBoxes[~ref];
+        if (!(lb.count & kLeafNoTest)) {
+            WideStats().leafTests++;
+            if (!SlabTest(r, lb.box, lb.box + 3, tMax)) return false;
+        }
+        cur = ref;
+        lslot = lb.first;
+        lcnt = int(lb.count & ~kLeafNoTest);
+        return true;
+    };
     auto popNext = [&]() {
         done = true;
         while (sp > 0) {
             E e = stack[--sp];
-            if (e.t < tMax) { cur = e.ref; done = false; break; }
+            if (e.t < tMax) {
+                if (e.ref >= 0) { cur = e.ref; done = false; break; }
+                if (enterLeaf(e.ref)) { done = false; break; }
+            }
         }
     };
     const bool flip = r.neg[2] != 0;
     const int cls = (r.neg[0] ^ int(flip)) | ((r.neg[1] ^ int(flip)) << 1);
-    if (!rootBox || SlabTest(r, rootBox, rootBox + 3, tMax)) cur = rootRef; else done = true;
+    if (!rootBox || SlabTest(r, rootBox, rootBox + 3, tMax)) {
+        if (rootRef >= 0) cur = rootRef;
+        else if (!enterLeaf(rootRef)) popNext();
+    } else
+        done = true;
     while (!done) {
         if (cur >= 0) {
             const Wide8 &w = hs.wide[cur];
@@ -131,8 +147,8 @@ inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, con
             for (int i = 0; i < 8; ++i) {
                 // near / far plane of each axis as the kernel picks them by address
                 const int nxp = r.neg[0] ? 3 : 0, nyp = r.neg[1] ? 4 : 1, nzp = r.neg[2] ? 5 : 2;
-                bool ok = SlabPlanesRegular(r, w.plane[nxp][i], w.plane[nyp][i], w.plane[nzp][i], w.plane[3 - nxp][i],
-                                            w.plane[5 - nyp][i], w.plane[7 - nzp][i], tm[i]) && tm[i] < tMaxS;
+                bool ok = WideChildTest(r, wr, w.plane[nxp][i], w.plane[nyp][i], w.plane[nzp][i], w.plane[3 - nxp][i],
+                                        w.plane[5 - nyp][i], w.plane[7 - nzp][i], tMaxS, tm[i]);
                 H |= unsigned(ok) << i;
             }
             const int nHit = __builtin_popcount(H);
@@ -148,7 +164,7 @@ inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, con
             sp += nHit;
             popNext();
         } else {
-            int slot = ~cur, cnt = int(hs.prims[slot].flags);
+            int slot = lslot, cnt = lcnt;
             WideStats().leaves++;
             WideStats().prims += cnt;
             for (int k = 0; k < cnt; ++k, ++slot) {
@@ -158,8 +174,8 @@ inline int TraceWide(const HostScene &hs, int rootRef, const float *rootBox, con
                     float o2[3], d2[3], tMax2;
                     InstanceRay(in.mInv, o[0], o[1], o[2], d[0], d[1], d[2], tMax, o2, d2, tMax2);
                     Best sub;
-                    int h = TraceWide(hs, in.rootWide, in.rootWide < 0 ? nullptr : in.rootBox, o2, d2, tMax2, any, sub,
-                                      int(s.tri));
+                    int h = TraceWide(hs, in.rootWide, in.rootWide < 0 ? nullptr : in.rootBox, in.rootBox, o2, d2, tMax2, any,
+                                      sub, int(s.tri));
                     if (h < 0) return -1;
                     if (any && h) return 1;
                     if (!any && sub.slot >= 0) {

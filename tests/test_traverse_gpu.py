@@ -180,3 +180,34 @@ def test_full_size_properties_1m_triangles(P):
     assert ((h3["mesh"] == 0xFFFFFFFF) | (h3["t"] <= hits["t"][hit])).all()
     assert not (agg.IntersectShadow(below[hit]) & ~(h3["mesh"] != 0xFFFFFFFF)).any()
     agg.close()
+
+
+def test_config2_full_size_bit_exact_vs_reference(P, refrun):
+    """BASELINE config 2 at its stated size against the compiled reference on the box's host cores: 1 M triangles,
+    2^24 primary + 2^24 shadow + 2^20 adversarial rays, closest-hit records and occlusion bits compared
+    with BVHAggregate::Intersect / IntersectP (cpu/aggregates.cpp:529-624) - 0 mismatches in (mesh, prim, instance,
+    t bits, b1, b2).  The primary batch goes through in 2^22-ray slices to bound the files handed to raycast_ref."""
+    sc = P.scenes.random_soup(1_000_000, seed=12111)
+    rs = refrun.RefScene(sc)
+    agg = P.B200Aggregate(sc)
+    total = 0
+    step = 1 << 22
+    for k in range(4):
+        rays = P.scenes.primary_rays(step, seed=100 + k)
+        ref, _ = rs.closest(rays)
+        mine = agg.IntersectClosest(rays)
+        assert hit_mismatches(mine, ref).sum() == 0
+        sh = P.scenes.shadow_rays(rays, mine, seed=200 + k)
+        occ_ref, _ = rs.any(sh)
+        assert (agg.IntersectShadow(sh) != occ_ref).sum() == 0
+        total += 2 * step
+    adv = P.scenes.adversarial_rays(sc, 1 << 20, seed=300)
+    ref, _ = rs.closest(adv)
+    mine = agg.IntersectClosest(adv, counters=True)
+    assert agg.trace_stats()["exact_rays"] > 0  # the axis-aligned ones took the exact binary walk
+    assert hit_mismatches(mine, ref).sum() == 0
+    occ_ref, _ = rs.any(adv)
+    assert (agg.IntersectShadow(adv) != occ_ref).sum() == 0
+    total += 2 * len(adv)
+    assert total >= (1 << 25) + (1 << 21)
+    agg.close()
