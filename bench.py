@@ -31,7 +31,31 @@ METRIC = "traversal_mrays_per_s"
 UNIT = "Mrays/s"
 
 
-DRAM_BYTES_PER_RAY_CLOSEST = (692695040 + 109081856) / (1 << 22)  # profiles/r01_headline_traffic_ncu.csv
+HEADLINE_NCU = os.path.join(ROOT, "profiles", "r02_headline_ncu.json")  # scripts/ncu_extract.py of the capture below
+
+
+def traversal_bytes(ts, any_hit=False):
+    """Algorithmic bytes per ray of a counted launch: the ray in, the record out, every node / leaf
+    box / primitive record the walk fetched.  wide walk: 256 B per Wide8 node, 32 B per leaf box, 48 B of each 64 B
+    primitive slot; binary walk: 32 B per box test (two per 64 B pair node), 48 B per primitive."""
+    r = max(ts["rays"], 1)
+    if ts["wide_nodes_visited"]:
+        node_bytes = 256 * ts["wide_nodes_visited"] + 32 * ts["leaf_boxes_tested"]
+    else:
+        node_bytes = 32 * ts["nodes_visited"]
+    return 28 + (1 if any_hit else 24) + (node_bytes + 48 * ts["prims_tested"]) / r
+
+
+def headline_ncu(kernel_substring):
+    """Counters of the headline kernel from the committed ncu capture of `scripts/r2_headline_prof.sh` (same scene, same
+    kernel build): DRAM bytes per ray, issue-slot utilisation, active lanes.  None when there is no capture."""
+    try:
+        for l in json.load(open(HEADLINE_NCU))["launches"]:
+            if kernel_substring in l["kernel"] and l.get("rays"):
+                return l
+    except Exception:
+        pass
+    return None
 
 
 def parse():
@@ -57,6 +81,8 @@ def parse():
     ap.add_argument("--config5-cpu-res", type=int, nargs=2, default=[960, 540], help="frame of the bounded reference sample")
     ap.add_argument("--config5-cpu-spp", type=int, default=4, help="spp of the bounded reference sample of config 5")
     ap.add_argument("--config3-cpu-spp", type=int, default=2, help="spp of the bounded pbrt_ref sample of config 3")
+    ap.add_argument("--config3-grid", type=int, default=224, help="tessellation of config 3's object definitions (2 * grid^2 triangles each)")
+    ap.add_argument("--parity-sample", type=int, default=1 << 20, help="rays of each kind compared with the reference inside the bench")
     return ap.parse_args()
 
 
@@ -134,6 +160,49 @@ def make_batches(P, agg, n, seed):
     return prim, shad
 
 
+def _bin(img, k):
+    h, w = img.shape[:2]
+    h2, w2 = h // k * k, w // k * k
+    return np.asarray(img, np.float64)[:h2, :w2].reshape(h2 // k, k, w2 // k, k, -1).mean(axis=(1, 3))
+
+
+def image_parity(img, ref, ref2=None):
+    """SURVEY 8(d)'s image gate at the size the reference sample was rendered at.  With a second reference image (the
+    next sampler seed): rRMSE(ours, ref) <= 1.25 x rRMSE(ref2, ref), per pixel and on 8 x 8 pixel bins (where the
+    Monte-Carlo noise is 8 x smaller), and |mean difference| <= 1 %.  Without: the path-for-path gate rRMSE <= 1e-3,
+    |mean difference| <= 1e-4 (the kernels consume the sampler dimensions in the CPU integrator's order)."""
+    def rr(a, b):
+        return float(np.sqrt(np.mean((np.asarray(a, np.float64) - b) ** 2)) / np.mean(b))
+    out = {"rrmse": rr(img, ref), "rrmse_binned8": rr(_bin(img, 8), _bin(ref, 8)),
+           "mean_rel_diff": float(abs(np.mean(img, dtype=np.float64) - np.mean(ref, dtype=np.float64)) / np.mean(ref, dtype=np.float64))}
+    if ref2 is not None:
+        out["noise_floor"] = rr(ref2, ref)
+        out["noise_floor_binned8"] = rr(_bin(ref2, 8), _bin(ref, 8))
+        out["gate"] = "rrmse <= 1.25 x noise_floor per pixel and on 8x8 bins, |mean diff| <= 1 %"
+        out["pass"] = bool(out["rrmse"] <= 1.25 * out["noise_floor"] and
+                           out["rrmse_binned8"] <= 1.25 * out["noise_floor_binned8"] and out["mean_rel_diff"] <= 0.01)
+    else:
+        out["gate"] = "path for path: rrmse <= 1e-3, |mean diff| <= 1e-4"
+        out["pass"] = bool(out["rrmse"] <= 1e-3 and out["mean_rel_diff"] <= 1e-4)
+    if not out["pass"]:
+        print("bench.py: IMAGE PARITY GATE FAILED: " + json.dumps(out), file=sys.stderr, flush=True)
+    return out
+
+
+def gpu_image_of_tables(P, tables, local, stream, spectral=False):
+    """One frame of the scene tables a host adaptor handed over (here: the reference's own dump of the very file the
+    reference rendered), all of its samples, on this rank's GPU."""
+    rsc = P.RenderScene(tables)
+    r = P.B200Renderer(rsc, device=local, stream=stream.cuda_stream)
+    try:
+        r.render()
+        if spectral:
+            return np.concatenate([r.image(), r.spectral_image()], axis=-1)
+        return r.image()
+    finally:
+        r.close()
+
+
 RENDER_CASE = "cornell_r512_s64"  # BASELINE.json configs[0]; tables in tests/golden (make_golden.py TABLE_CASES)
 RENDER_KW = dict(res=512, spp=64, maxdepth=5, lightsampler="power", seed=0)
 
@@ -145,7 +214,7 @@ class _DevArray:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
-def render_cpu_reference(args, P):
+def render_cpu_reference(args, P, local, stream):
     """pbrt_ref (the reference's own main, CPU PathIntegrator) on a bounded sample of config 1:
     the same scene and resolution at --render-cpu-spp samples per pixel, all host cores."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -156,9 +225,12 @@ def render_cpu_reference(args, P):
     with tempfile.TemporaryDirectory() as tmp:
         pbrt, pfm = os.path.join(tmp, "c.pbrt"), os.path.join(tmp, "c.pfm")
         P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
-        _, secs = refrun.render(pbrt, pfm)
+        ref, secs = refrun.render(pbrt, pfm)
+        tables = P.scenes.load_b2rs(refrun.dump_scene(pbrt, os.path.join(tmp, "c.b2rs")))
+    parity = image_parity(gpu_image_of_tables(P, tables, local, stream), ref)
+    parity["sample"] = f"{kw['res']}x{kw['res']}, {kw['spp']} spp, same sampler seed"
     n = kw["res"] * kw["res"] * kw["spp"]
-    return {"value": n / secs * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
+    return {"value": n / secs * 1e-6, "parity": parity, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
             "seconds": secs,
             "sample": f"Cornell {kw['res']}x{kw['res']} at {kw['spp']} spp (config 1 is 64 spp), wall clock of the "
                       f"whole pbrt_ref process incl. parse + BVH build (36 triangles)"}
@@ -214,7 +286,7 @@ def render_section(args, P, torch, dist, rank, world, local, stream, barrier):
                "rays_per_frame": (st["closest_rays"] + st["shadow_rays"]) * world,
                "launches_per_frame": st["kernel_launches"], "image_mean": float(img.mean())}
         if not args.no_cpu_baseline:
-            out["cpu_baseline"] = render_cpu_reference(args, P)
+            out["cpu_baseline"] = render_cpu_reference(args, P, local, stream)
     r.close()
     return out
 
@@ -272,11 +344,17 @@ def config3_shadow_rays(P, rsc, prim, hits, seed):
 
 
 def config3_section(args, P, torch, dist, rank, world, local, stream, barrier):
-    """BASELINE configs[2], the north_star's headline scene: ~10 M instanced triangles (32 definitions x 2048
-    triangles x 4883 placements), glass / metal / coated / diffuse, 2048 emitters through the light BVH.
+    """BASELINE configs[2], the north_star's headline scene at the size SURVEY 8(d) fixes: 100 object definitions x
+    100 352 triangles (10 M unique) placed 1000 times (100 M instanced), glass / metal / coated / diffuse, 20 000 emitters
+    through the light BVH.  The committed tables hold the scene at a coarse tessellation; the definitions are
+    re-tessellated here by the scene's own generator (scenes.config3_refine).
     (a) traversal of camera + shadow rays, weak scaling like the main line; (b) the frame at
     --config3-spp of its 1024 spp per step, sample stripes over the ranks."""
-    rsc = P.RenderScene.load(os.path.join(ROOT, "tests", "golden", CONFIG3_CASE + ".b2rs"))
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden
+    full = make_golden.CONFIG3_FULL
+    rsc = P.RenderScene(P.scenes.config3_refine(P.scenes.load_b2rs(os.path.join(ROOT, "tests", "golden", CONFIG3_CASE + ".b2rs")),
+                                                full["n_objects"], full["n_instances"], args.config3_grid))
     geo = rsc.geometry
     agg = P.B200Aggregate(geo, device=local, stream=stream.cuda_stream)
     st = agg.stats()
@@ -351,20 +429,25 @@ def config3_section(args, P, torch, dist, rank, world, local, stream, barrier):
     w, h = rsc.resolution
     ns = w * h * spp * args.steps
     peak, _ = peaks()
-    NODE_B, PRIM_B = 32, 48
-    bytes_closest = 28 + 24 + (NODE_B * tc["nodes_visited"] + PRIM_B * tc["prims_tested"]) / tc["rays"]
-    ntri = int(sum(len(m.indices) for m in geo.meshes if m.object < 0) +
-               sum(sum(len(m.indices) for m in geo.meshes if m.object == i.object) for i in geo.instances))
-    out = {"workload": f"config3: {ntri} instanced triangles ({len(geo.instances)} placements of "
+    bytes_closest = traversal_bytes(tc)
+    per_object = {}
+    for m in geo.meshes:
+        if m.object >= 0:
+            per_object[m.object] = per_object.get(m.object, 0) + len(m.indices)
+    ntri = int(sum(len(m.indices) for m in geo.meshes if m.object < 0) + sum(per_object[i.object] for i in geo.instances))
+    nunique = int(sum(len(m.indices) for m in geo.meshes))
+    out = {"workload": f"config3: {nunique} unique / {ntri} instanced triangles ({len(geo.instances)} placements of "
                        f"{len(set(i.object for i in geo.instances))} object definitions), {len(rsc.d['lights_i'])} lights, "
                        f"{w}x{h}; traversal: {n} camera rays (jittered, in the order a pass generates them: raster order, sample after sample) + {n} shadow rays from their hits towards random emitters per step per rank",
-           "triangles": ntri,
+           "triangles": ntri, "unique_triangles": nunique,
            "traversal": {"metric": METRIC, "unit": UNIT,
                          "value": 2 * n * world / ((ms_closest + ms_any) * 1e-3) * 1e-6,
                          "closest_mrays_per_s": n * world / (ms_closest * 1e-3) * 1e-6,
                          "any_mrays_per_s": n * world / (ms_any * 1e-3) * 1e-6,
-                         "nodes_per_ray": tc["nodes_visited"] / tc["rays"], "prims_per_ray": tc["prims_tested"] / tc["rays"],
-                         "nodes_per_ray_any": ta["nodes_visited"] / ta["rays"],
+                         "box_tests_per_ray": tc["nodes_visited"] / tc["rays"], "prims_per_ray": tc["prims_tested"] / tc["rays"],
+                         "wide_nodes_per_ray": tc["wide_nodes_visited"] / tc["rays"],
+                         "leaf_boxes_per_ray": tc["leaf_boxes_tested"] / tc["rays"],
+                         "box_tests_per_ray_any": ta["nodes_visited"] / ta["rays"],
                          "bytes_per_ray": bytes_closest,
                          "roofline_frac": bytes_closest * n / (ms_closest * 1e-3) * 1e-9 / peak,
                          "hit_fraction": hit_frac, "occluded_fraction": occ_frac,
@@ -378,28 +461,60 @@ def config3_section(args, P, torch, dist, rank, world, local, stream, barrier):
                       "rays_per_frame": (rst["closest_rays"] + rst["shadow_rays"]) * world,
                       "launches_per_frame": rst["kernel_launches"], "image_mean": float(img.mean())}}
     if not args.no_cpu_baseline:
-        out["render"]["cpu_baseline"] = config3_cpu_reference(args, P)
+        out["render"]["cpu_baseline"] = config3_cpu_reference(args, P, local, stream)
+        out["traversal"]["parity"] = config3_traversal_parity(args, P, geo, prim, shad, local, stream)
     return out
 
 
-def config3_cpu_reference(args, P):
-    """pbrt_ref on a bounded sample of config 3: the whole scene and frame at --config3-cpu-spp samples per pixel."""
+def config3_traversal_parity(args, P, geo, prim, shad, local, stream):
+    """Hit records of a sample of the timed batches against the reference's BVHAggregate (raycast_ref builds its own
+    two-level BVH over the 10 M unique triangles): 0 mismatches in (mesh, prim, instance, t bits, b1, b2)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import refrun
+    from conftest import hit_mismatches
+    if not refrun.available():
+        return {"mismatches": None, "sample": "oracle/_ref not built"}
+    m = min(args.parity_sample, len(prim))
+    rs = refrun.RefScene(geo)
+    agg = P.B200Aggregate(geo, device=local, stream=stream.cuda_stream)
+    ref, _ = rs.closest(prim[:m])
+    bad = int(hit_mismatches(agg.IntersectClosest(prim[:m]), ref).sum())
+    occ, _ = rs.any(shad[:m])
+    bad_any = int((agg.IntersectShadow(shad[:m]) != occ).sum())
+    agg.close()
+    if bad or bad_any:
+        print(f"bench.py: CONFIG 3 TRAVERSAL PARITY FAILED: {bad} closest / {bad_any} any-hit mismatches", file=sys.stderr, flush=True)
+    return {"mismatches": bad + bad_any, "rays": 2 * m,
+            "sample": f"first {m} camera + {m} shadow rays of the timed batches vs oracle/_ref/raycast_ref, bit-exact compare"}
+
+
+def config3_cpu_reference(args, P, local, stream):
+    """pbrt_ref on a bounded sample of config 3: the whole full-size scene (object definitions as binary PLY) and frame at
+    --config3-cpu-spp samples per pixel, sampler seeds 0 and 1; the GPU renders the reference's own dump of the seed-0
+    file and is held to SURVEY 8(d)'s noise-floor gate."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refrun
     sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
     if not refrun.render_available():
         return {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
     import make_golden
-    kw = dict(make_golden.CONFIG3_FULL, spp=args.config3_cpu_spp)
+    kw = dict(make_golden.CONFIG3_FULL, grid=args.config3_grid, spp=args.config3_cpu_spp)
     with tempfile.TemporaryDirectory() as tmp:
         pbrt, pfm = os.path.join(tmp, "c3.pbrt"), os.path.join(tmp, "c3.pfm")
-        P.scenes.config3_pbrt(pbrt, out=pfm, **kw)
-        _, secs = refrun.render(pbrt, pfm)
+        os.makedirs(os.path.join(tmp, "ply"))
+        P.scenes.config3_pbrt(pbrt, out=pfm, ply_dir=os.path.join(tmp, "ply"), **kw)
+        ref, secs = refrun.render(pbrt, pfm)
+        tables = P.scenes.load_b2rs(refrun.dump_scene(pbrt, os.path.join(tmp, "c3.b2rs"), bvh=False))
+        P.scenes.config3_pbrt(pbrt, out=pfm, ply_dir=os.path.join(tmp, "ply"), **dict(kw, seed=1))
+        ref2, _ = refrun.render(pbrt, pfm)
+    parity = image_parity(gpu_image_of_tables(P, tables, local, stream), ref, ref2)
+    parity["sample"] = f"{kw['res'][0]}x{kw['res'][1]}, {kw['spp']} spp, seeds 0 / 1 for the floor"
     n = kw["res"][0] * kw["res"][1] * kw["spp"]
     return {"value": n / secs * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
-            "seconds": secs,
-            "sample": f"the config-3 scene at {kw['res'][0]}x{kw['res'][1]}, {kw['spp']} spp (config 3 is 1024 spp), wall "
-                      f"clock of the whole pbrt_ref process incl. parse + BVH builds"}
+            "seconds": secs, "parity": parity,
+            "sample": f"the full-size config-3 scene at {kw['res'][0]}x{kw['res'][1]}, {kw['spp']} spp (config 3 is 1024 spp), wall "
+                      f"clock of the whole pbrt_ref process incl. parse + BVH builds over 10 M triangles"}
 
 
 CONFIG4_CASE = "config4_full"  # BASELINE.json configs[3]; tables in tests/golden (make_golden.py CONFIG4_FULL)
@@ -457,11 +572,11 @@ def config4_section(args, P, torch, dist, rank, world, local, stream, barrier):
            "rays_per_frame": (st["closest_rays"] + st["shadow_rays"]) * world,
            "launches_per_frame": st["kernel_launches"], "image_mean": float(img.mean())}
     if not args.no_cpu_baseline:
-        out["cpu_baseline"] = config4_cpu_reference(args, P)
+        out["cpu_baseline"] = config4_cpu_reference(args, P, local, stream)
     return out
 
 
-def config4_cpu_reference(args, P):
+def config4_cpu_reference(args, P, local, stream):
     """The reference's render loop + Film::GetImage (dumpscene_ref --render: the oracle build has no EXR writer,
     which pbrt_ref's spectral film would need) on a bounded sample of config 4: the whole frame at
     --config4-cpu-spp samples per pixel, all host cores."""
@@ -475,9 +590,13 @@ def config4_cpu_reference(args, P):
     with tempfile.TemporaryDirectory() as tmp:
         pbrt = os.path.join(tmp, "c4.pbrt")
         P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), **kw)
-        _, _, secs = refrun.render_channels(pbrt)
+        ref, _, secs = refrun.render_channels(pbrt)
+        tables = P.scenes.load_b2rs(refrun.dump_scene(pbrt, os.path.join(tmp, "c4.b2rs")))
+    # path for path (no smooth dielectric in this scene): RGB + the 31 band channels
+    parity = image_parity(gpu_image_of_tables(P, tables, local, stream, spectral=True), ref)
+    parity["sample"] = f"{kw['res']}x{kw['res']}, {kw['spp']} spp, RGB + {ref.shape[-1] - 3} band channels"
     n = kw["res"] * kw["res"] * kw["spp"]
-    return {"value": n / secs * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
+    return {"value": n / secs * 1e-6, "parity": parity, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
             "seconds": secs,
             "sample": f"the config-4 scene at {kw['res']}x{kw['res']}, {kw['spp']} spp (config 4 is 256 spp), wall clock of "
                       f"the whole process incl. parse and the camera's exit-pupil table (64 x 2^20 lens traces)"}
@@ -537,11 +656,11 @@ def config5_section(args, P, torch, dist, rank, world, local, stream, barrier):
            "rays_per_frame": (st["closest_rays"] + st["shadow_rays"]) * world,
            "launches_per_frame": st["kernel_launches"], "image_mean": float(img.mean())}
     if not args.no_cpu_baseline:
-        out["cpu_baseline"] = config5_cpu_reference(args, P)
+        out["cpu_baseline"] = config5_cpu_reference(args, P, local, stream)
     return out
 
 
-def config5_cpu_reference(args, P):
+def config5_cpu_reference(args, P, local, stream):
     """pbrt_ref (CPU VolPathIntegrator) on a bounded sample of config 5: the same scene and grid, a smaller frame at
     --config5-cpu-spp; the parse of the inline grid (16.7 M values) is timed apart with an 8x8, 1 spp run and
     subtracted."""
@@ -556,11 +675,19 @@ def config5_cpu_reference(args, P):
         P.scenes.config5_pbrt(pbrt, out=pfm, res=(8, 8), spp=1, grid=args.config5_grid, density=dens)
         _, setup = refrun.render(pbrt, pfm)
         P.scenes.config5_pbrt(pbrt, out=pfm, res=(w, h), spp=args.config5_cpu_spp, grid=args.config5_grid, density=dens)
-        _, secs = refrun.render(pbrt, pfm)
+        ref, secs = refrun.render(pbrt, pfm)
+        # tables of the same frame from the reference's parser (small grid: the dump keeps the frame, the full grid is
+        # swapped in as in the timed section), and the next seed for the noise floor
+        P.scenes.config5_pbrt(pbrt, out=pfm, res=(w, h), spp=args.config5_cpu_spp, grid=16)
+        tables = P.scenes.with_density_grid(P.scenes.load_b2rs(refrun.dump_scene(pbrt, os.path.join(tmp, "c5.b2rs"))), dens)
+        P.scenes.config5_pbrt(pbrt, out=pfm, res=(w, h), spp=args.config5_cpu_spp, grid=args.config5_grid, density=dens, seed=1)
+        ref2, _ = refrun.render(pbrt, pfm)
+    parity = image_parity(gpu_image_of_tables(P, tables, local, stream), ref, ref2)
+    parity["sample"] = f"{w}x{h}, {args.config5_cpu_spp} spp, seeds 0 / 1 for the floor"
     n = w * h * args.config5_cpu_spp
     render = max(secs - setup, 1e-3)
     return {"value": n / render * 1e-6, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
-            "seconds": render, "setup_seconds": setup,
+            "seconds": render, "setup_seconds": setup, "parity": parity,
             "sample": f"the config-5 scene ({args.config5_grid}^3 grid) at {w}x{h}, {args.config5_cpu_spp} spp (config 5 is "
                       f"1920x1080, 512 spp); wall clock of pbrt_ref minus that of an 8x8 1-spp run (parse + majorant grid)"}
 
@@ -644,9 +771,7 @@ def main():
     tc = agg.trace_stats()
     agg.IntersectShadow(shad[sample], counters=True)
     ta = agg.trace_stats()
-    NODE_B, PRIM_B = 32, 48
-    bytes_closest = 28 + 24 + (NODE_B * tc["nodes_visited"] + PRIM_B * tc["prims_tested"]) / tc["rays"]
-    bytes_any = 28 + 1 + (NODE_B * ta["nodes_visited"] + PRIM_B * ta["prims_tested"]) / ta["rays"]
+    bytes_closest, bytes_any = traversal_bytes(tc), traversal_bytes(ta, any_hit=True)
 
     # ---- device-resident timing (value)
     d_prim = torch.from_numpy(prim).cuda()
@@ -700,6 +825,10 @@ def main():
     if rank == 0:
         assert np.array_equal(h_hits.numpy(), d_hits.cpu().numpy()) and np.array_equal(h_occ.numpy(), d_occ.cpu().numpy())
 
+    cpu_base = None
+    if rank == 0 and not args.no_cpu_baseline:
+        cpu_base = cpu_baseline(args, P, sc, prim, shad, agg)
+
     render = None
     if not args.no_render:
         render = render_section(args, P, torch, dist, rank, world, local, stream, barrier)
@@ -736,6 +865,35 @@ def main():
         rays_total = 2.0 * n * world * args.steps
         value = rays_total / (total_ms * 1e-3) * 1e-6
         ach = bytes_closest * n / (ms_closest * 1e-3) * 1e-9
+        wide = tc["wide_nodes_visited"] > 0
+        cap = headline_ncu("TraverseWideKernel<0" if wide else "TraverseBinaryKernel<0") if args.tris == 1_000_000 else None
+        roofline = {
+            # what bounds the kernel according to ncu (profiles/): instruction issue at ~45 % lane occupancy plus the L1
+            # tag stage (one wavefront per lane per 32-byte node fetch); the tree is L2-resident, HBM is almost idle
+            "bound": "issue", "kernel": "closest-hit traversal (%s walk)" % ("8-wide" if wide else "binary"),
+            # contract figure: ALGORITHMIC bytes per launch / CUDA-event time, against the measured HBM copy peak.  These
+            # bytes are served by L2, so this is an L2-level rate; `frac_dram` below is the HBM-level one.
+            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src,
+            "bytes_per_ray": bytes_closest, "bytes_per_ray_any": bytes_any, "compulsory_bytes_per_ray": 52,
+            "box_tests_per_ray": tc["nodes_visited"] / tc["rays"],
+            "nodes_per_ray": (tc["wide_nodes_visited"] if wide else tc["nodes_visited"] / 2) / tc["rays"],
+            "node_bytes": 256 if wide else 64,
+            "leaf_boxes_per_ray": tc["leaf_boxes_tested"] / tc["rays"],
+            "prims_per_ray": tc["prims_tested"] / tc["rays"],
+            "traffic": None, "frac_dram": None,
+        }
+        if cap:
+            dram = cap["dram_bytes_per_ray"]
+            roofline.update({
+                # dram__bytes_read.sum + dram__bytes_write.sum of this kernel per ray (ncu --set full capture of the same
+                # kernel on the same scene, file below) x this launch's rays
+                "traffic": dram * n, "traffic_bytes_per_ray": dram, "traffic_source": os.path.relpath(HEADLINE_NCU, ROOT),
+                "frac_dram": dram * n / (ms_closest * 1e-3) * 1e-9 / peak,
+                "issue_slots_busy": cap.get("issue_active_pct", 0.0) / 100.0,
+                "active_threads_per_warp": cap.get("active_threads_per_warp"),
+                "issue_x_lanes": cap.get("issue_active_pct", 0.0) / 100.0 * (cap.get("active_threads_per_warp") or 0.0) / 32.0,
+                "l1tex_throughput_pct": cap.get("l1tex_throughput_pct"), "l2_throughput_pct": cap.get("l2_throughput_pct"),
+                "warp_instructions_per_ray": cap.get("warp_instructions_per_ray")})
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -743,21 +901,7 @@ def main():
             "config": workload_config(args),
             "closest_mrays_per_s": n * world / (ms_closest * 1e-3) * 1e-6,
             "any_mrays_per_s": n * world / (ms_any * 1e-3) * 1e-6,
-            "roofline": {"bound": "hbm", "kernel": "closest-hit traversal", "achieved": ach, "peak": peak,
-                         "unit": "GB/s", "frac": ach / peak,
-                         # DRAM bytes per launch: dram__bytes_read.sum + dram__bytes_write.sum of this kernel from ncu
-                         # (profiles/r01_headline_traffic_ncu.csv: 801.8 MB for a 2^22-ray launch on this scene =
-                         # 191.2 B/ray, against 52 B/ray compulsory and ~3.7 KB/ray algorithmic, which the 126 MB
-                         # L2 serves: lts__t_bytes = 3.97 KB/ray), scaled to this launch's ray count
-                         "traffic": (DRAM_BYTES_PER_RAY_CLOSEST * n if args.tris == 1_000_000 else None),
-                         "traffic_note": "ncu dram bytes per ray (2^22-ray launch) x rays per launch; the algorithmic "
-                                         "bytes are served by L2 (lts__t_bytes 3.97 KB/ray), so `achieved` is an "
-                                         "L2-level rate reported against the HBM peak as the contract asks",
-                         "peak_source": peak_src,
-                         "bytes_per_ray": bytes_closest, "bytes_per_ray_any": bytes_any,
-                         "nodes_per_ray": tc["nodes_visited"] / tc["rays"],
-                         "prims_per_ray": tc["prims_tested"] / tc["rays"],
-                         "compulsory_bytes_per_ray": 52},
+            "roofline": roofline,
             "e2e": {"value": rays_total / e2e_s * 1e-6, "unit": UNIT,
                     "h2d_bytes_per_step": 2 * n * 28, "d2h_bytes_per_step": n * 24 + n},
             "gpu_launches": 2 * args.steps,
@@ -769,8 +913,9 @@ def main():
             "scene": {"bvh2_nodes": st["n_bvh2_nodes"], "wide_nodes": st["n_wide_nodes"],
                       "device_bytes": st["device_bytes"], "build_s": st["build_seconds"]},
         }
-        if not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(args, P, sc, prim, shad)
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+            line["parity"] = cpu_base.pop("parity")
         print(json.dumps(line), flush=True)
     if agg is not None:
         agg.close()
@@ -779,21 +924,35 @@ def main():
         dist.destroy_process_group()
 
 
-def cpu_baseline(args, P, sc, prim, shad):
-    """The reference's own BVHAggregate (oracle/_ref/raycast_ref) on a bounded sample, all host cores."""
+def cpu_baseline(args, P, sc, prim, shad, agg):
+    """The reference's own BVHAggregate (oracle/_ref/raycast_ref) on a bounded sample, all host cores; its answers are
+    also the bit-exactness check of the GPU's records for the same rays (`parity`)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
     import refrun
     if not refrun.available():
-        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built",
+                "parity": {"mismatches": None}}
+    from conftest import hit_mismatches
     m = min(args.cpu_sample, prim.shape[0])
     rs = refrun.RefScene(sc)
-    _, ic = rs.closest(prim[:m], nthreads=0, reps=2)
-    _, ia = rs.any(shad[:m], nthreads=0, reps=2)
+    ref, ic = rs.closest(prim[:m], nthreads=0, reps=2)
+    occ, ia = rs.any(shad[:m], nthreads=0, reps=2)
+    bad = int(hit_mismatches(agg.IntersectClosest(prim[:m]), ref).sum()) + int((agg.IntersectShadow(shad[:m]) != occ).sum())
+    adv = P.scenes.adversarial_rays(sc, min(args.parity_sample, 1 << 20), seed=300)
+    ref_adv, _ = rs.closest(adv)
+    bad += int(hit_mismatches(agg.IntersectClosest(adv), ref_adv).sum())
+    if bad:
+        print(f"bench.py: TRAVERSAL PARITY FAILED: {bad} mismatches against the reference", file=sys.stderr, flush=True)
     sec = ic["seconds"] + ia["seconds"]
     return {"value": 2 * m / sec * 1e-6, "unit": UNIT, "cores": ic["threads"], "kind": "reference",
             "closest_mrays_per_s": ic["mrays_per_s"], "any_mrays_per_s": ia["mrays_per_s"],
             "sample": f"first {m} primary + {m} shadow rays of the timed batches, best of 2 passes, "
-                      f"BVH build excluded ({ic['build_s']:.2f} s)"}
+                      f"BVH build excluded ({ic['build_s']:.2f} s)",
+            "parity": {"mismatches": bad, "rays": 2 * m + len(adv),
+                       "sample": f"the CPU sample's {m} primary + {m} shadow rays and {len(adv)} adversarial rays (through vertices / "
+                                 f"edges, axis-aligned, origins in bounding planes): (mesh, prim, instance, t bits, b1, b2) and "
+                                 f"occlusion bits against BVHAggregate::Intersect / IntersectP"}}
 
 
 if __name__ == "__main__":

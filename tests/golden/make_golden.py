@@ -104,7 +104,13 @@ TABLE_CASES = {
 }
 # BASELINE.json configs[2] (scenes.config3_pbrt): full size as tables only (bench.py), and in miniature with
 # reference images (noise-gated: the scene has smooth glass, see NOISE_GATED)
-CONFIG3_FULL = dict(n_objects=32, grid=32, n_instances=4883, n_lights=1024, res=(1920, 1080), spp=1024, maxdepth=5)
+# Full size: 100 object definitions x 2 * 224^2 = 100 352 triangles (10 M unique), 1000 instances
+# (100 M instanced triangles), 10 000 emissive quads = 20 000 lights.  The committed tables are the reference's dump of
+# the scene at a coarse tessellation (grid 4); scenes.config3_refine() re-tessellates the object definitions to
+# CONFIG3_FULL_GRID with the same generator (checked there, and against a direct dump by tests/test_render_cpu.py).
+CONFIG3_FULL = dict(n_objects=100, grid=4, n_instances=1000, n_lights=10000, res=(1920, 1080), spp=1024, maxdepth=5,
+                    scale=(2.0, 4.5))
+CONFIG3_FULL_GRID = 224
 CONFIG3_SMALL = dict(n_objects=8, grid=12, n_instances=300, n_lights=96, res=(96, 54), spp=16, maxdepth=5)
 # BASELINE.json configs[3] (scenes.config4_pbrt): RealisticCamera + 31-band SpectralFilm.  Full size as tables
 # only (bench.py renders a bounded reference sample on the spot); in miniature with the reference's image.
@@ -176,6 +182,38 @@ def make_config5_goldens(P, refrun, out):
         refrun.dump_scene(pbrt, os.path.join(out, "config5_full.b2rs"))
 
 
+# The noise-gated cases again where the gate means something (at 16 spp the floor is ~0.35, so 0.44 passed):
+# 1024 spp on a small frame, two reference seeds, floor ~0.03-0.05.  A wrong BSDF lobe or a biased roulette shows up as a
+# multiple of that.  name -> (generator, arguments)
+TIGHT_CASES = {
+    "tight_glass": ("cornell", dict(res=32, spp=4096, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass"))),
+    "tight_metal2": ("cornell", dict(res=32, spp=1024, maxdepth=4, boxes=("conductor_reflectance", "dielectric_rough"),
+                                     regularize=True)),
+    "tight_coated": ("cornell", dict(res=32, spp=1024, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough"))),
+    "tight_alpha": ("cornell", dict(res=32, spp=1024, maxdepth=5, alpha=True)),
+    "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
+    "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),
+}
+
+
+def make_tight_goldens(P, refrun, out):
+    import tempfile
+    gen = {"cornell": P.scenes.cornell_pbrt, "config3": P.scenes.config3_pbrt, "config5": P.scenes.config5_pbrt}
+    for name, (kind, kw) in TIGHT_CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            pbrt, pfm = os.path.join(tmp, name + ".pbrt"), os.path.join(tmp, name + ".pfm")
+            imgs = []
+            for seed, suffix in ((0, "_ref.npy"), (1, "_ref2.npy")):
+                gen[kind](pbrt, out=pfm, **dict(kw, seed=kw.get("seed", 0) + seed))
+                if seed == 0:
+                    refrun.dump_scene(pbrt, os.path.join(out, name + ".b2rs"))
+                img, secs = refrun.render(pbrt, pfm)
+                np.save(os.path.join(out, name + suffix), img.astype(np.float32))
+                imgs.append(img.astype(np.float64))
+            floor = np.sqrt(np.mean((imgs[1] - imgs[0]) ** 2)) / imgs[0].mean()
+            print(name, imgs[0].shape, "mean", imgs[0].mean(), f"noise floor {floor:.4f}", f"{secs:.1f}s")
+
+
 def make_render_goldens(P, refrun, out):
     import tempfile
     pick = os.environ.get("B200PT_GOLDEN_CASES")  # comma-separated names: regenerate only these image cases
@@ -222,7 +260,7 @@ if __name__ == "__main__":
     import pbrt_v4_b200 as P
     import refrun
     out = os.path.dirname(os.path.abspath(__file__))
-    known = ("--omni-only", "--config4-only", "--config5-only", "--render-only")
+    known = ("--omni-only", "--config4-only", "--config5-only", "--render-only", "--tight-only")
     for a in sys.argv[1:]:
         if a not in known and not a.startswith("--only="):
             sys.exit(f"unknown argument {a}; known: {known}, --only=name,...  (no argument regenerates every fixture)")
@@ -230,6 +268,9 @@ if __name__ == "__main__":
         pass
     elif "--config5-only" in sys.argv:
         make_config5_goldens(P, refrun, out)
+        sys.exit(0)
+    if "--tight-only" in sys.argv:
+        make_tight_goldens(P, refrun, out)
         sys.exit(0)
     if "--omni-only" in sys.argv:
         make_omni_goldens(P, refrun, out)
@@ -243,6 +284,7 @@ if __name__ == "__main__":
             make_config4_goldens(P, refrun, out)
             make_omni_goldens(P, refrun, out)
             make_config5_goldens(P, refrun, out)
+            make_tight_goldens(P, refrun, out)
     if "--render-only" in sys.argv:
         sys.exit(0)
     only = [a.split("=", 1)[1].split(",") for a in sys.argv if a.startswith("--only=")]

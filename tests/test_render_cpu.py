@@ -232,3 +232,15 @@ def test_majorant_grid_mirror(P):
     """scenes.majorant_grid (used to build full-size config-5 tables) reproduces the host's MajorantGrid."""
     d = P.scenes.load_b2rs(os.path.join(GOLD, "config5_small.b2rs"))
     np.testing.assert_array_equal(P.scenes.majorant_grid(d["medium_density_0"]), d["medium_majorants_0"])
+
+
+@pytest.mark.parametrize("name", ["tight_metal2", "tight_coated", "tight_alpha", "tight_glass"])
+def test_tight_noise_gate(P, rendercheck, name):
+    """The 16-spp noise-gated families at 1024-4096 spp on a 32 x 32 frame (floor 2-5 %, make_golden.py TIGHT_CASES):
+    the host loop over the kernels' headers inside SURVEY 8(d)'s gate where the gate can tell a wrong lobe."""
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref, ref2 = (np.load(os.path.join(GOLD, name + s)) for s in ("_ref.npy", "_ref2.npy"))
+    img = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
+    ok, floor = noise_gate(img, ref, ref2)
+    assert floor <= 0.05
+    assert ok, (rrmse(img, ref), floor)
