@@ -95,7 +95,9 @@ int b200pt_context_create(int device, b200pt_ctx **out) {
     c->ownStream = true;
     const char *mode = getenv("B200PT_TRAVERSAL");
     c->simpleKernel = mode && std::string(mode) == "simple";
-    c->wideKernel = !(mode && (std::string(mode) == "binary" || std::string(mode) == "pair"));
+    // default: the exact binary walk - measured faster than the 8-wide walk on every BASELINE config (profiles/r02_*);
+    // B200PT_TRAVERSAL=wide selects the 8-wide walk
+    c->wideKernel = mode && std::string(mode) == "wide";
     if (const char *v = getenv("B200PT_REFILL_MIN")) c->refillMin = std::max(1, std::min(32, atoi(v)));
     if (const char *v = getenv("B200PT_NODE_MIN")) c->nodeMin = std::max(0, std::min(32, atoi(v)));
     *out = c;

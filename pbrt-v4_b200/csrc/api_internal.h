@@ -30,7 +30,7 @@ struct b200pt_ctx {
     // scheduling knobs of the persistent kernel (B200PT_REFILL_MIN / B200PT_NODE_MIN override)
     int refillMin = 4, nodeMin = 16;
     bool simpleKernel = false;  // B200PT_TRAVERSAL=simple: the one-thread-per-ray parity kernel
-    bool wideKernel = true;     // B200PT_TRAVERSAL=binary: the exact binary kernel for every ray
+    bool wideKernel = false;    // B200PT_TRAVERSAL=wide: the 8-wide walk (irregular rays still take the binary kernel)
     // [0] = count, [1..] = indices of the rays the wide kernel handed to the exact binary kernel (grow-only)
     int *dExact = nullptr;
     size_t dExactCap = 0;

@@ -113,6 +113,34 @@ B2_HD void RaySetup(RayCtx &r, float ox, float oy, float oz, float dx, float dy,
     r.Sz = B2_DIV(1.f, pdz);
 }
 
+#if defined(__CUDACC__)
+// A ray's derived terms as four stack entries, and back: leaving an object instance restores the parent ray's
+// context instead of dividing six times again (RaySetup).
+__device__ __forceinline__ void RaySave(const RayCtx &r, int2 &c0, int2 &c1, int2 &c2, int2 &c3) {
+    c0 = make_int2(__float_as_int(r.ix), __float_as_int(r.iy));
+    c1 = make_int2(__float_as_int(r.iz), __float_as_int(r.Sx));
+    c2 = make_int2(__float_as_int(r.Sy), __float_as_int(r.Sz));
+    c3 = make_int2(r.kx | (r.ky << 2) | (r.kz << 4), 0);
+}
+__device__ __forceinline__ void RayRestore(RayCtx &r, float ox, float oy, float oz, float dx, float dy, float dz, int2 c0, int2 c1, int2 c2,
+                      int2 c3) {
+    r.ox = ox; r.oy = oy; r.oz = oz;
+    r.dx = dx; r.dy = dy; r.dz = dz;
+    r.ix = __int_as_float(c0.x);
+    r.iy = __int_as_float(c0.y);
+    r.iz = __int_as_float(c1.x);
+    r.Sx = __int_as_float(c1.y);
+    r.Sy = __int_as_float(c2.x);
+    r.Sz = __int_as_float(c2.y);
+    r.neg[0] = r.ix < 0;
+    r.neg[1] = r.iy < 0;
+    r.neg[2] = r.iz < 0;
+    r.kx = c3.x & 3;
+    r.ky = (c3.x >> 2) & 3;
+    r.kz = (c3.x >> 4) & 3;
+}
+#endif
+
 // Bounds3::IntersectP with precomputed invDir/dirIsNeg.  Branch-free: the reference's two early
 // `return false` only skip work, so evaluating everything and AND-ing the conditions gives the same
 // boolean (selects keep the reference's NaN behaviour: `a > b ? a : b`, not fmax).

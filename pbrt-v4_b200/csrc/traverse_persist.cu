@@ -123,8 +123,11 @@ TraverseBinaryKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200
             int2 e = pop();
             if (INST && e.x < -(1 << 30)) {  // the way back out of an instance
                 int2 saved = pop();
+                // the parent ray: o, d from the ray buffer, everything derived from them (three 1/d, the shear
+                // terms: six divisions) from the four entries stacked under the return entry
                 const float *q = rays + 7ll * rayIdx;
-                RaySetup(r, q[0], q[1], q[2], q[3], q[4], q[5]);
+                const int2 c3 = pop(), c2 = pop(), c1 = pop(), c0 = pop();
+                RayRestore(r, q[0], q[1], q[2], q[3], q[4], q[5], c0, c1, c2, c3);
                 if (!instHit) tMax = __int_as_float(saved.y);
                 curInst = -1;
                 if (saved.x > 0) {
@@ -195,9 +198,14 @@ TraverseBinaryKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200
                 // near child: visited now, so the whole test applies now.  far child: stacked on the
                 // tMax-independent part only; `tFar < tMax` is decided when it is popped (popNext).
                 bool hNear = (neg ? h1 : h0) & (tNear < tMax), hFar = neg ? h0 : h1;
-                if (hFar) push(farRef, __float_as_int(tFar));
-                if (hNear) enter(nearRef);
-                else popNext();
+                if (hNear) {
+                    if (hFar) push(farRef, __float_as_int(tFar));
+                    enter(nearRef);
+                } else if (hFar & (tFar < tMax)) {
+                    enter(farRef);  // the reference pops it next, with this very tMax: no stack round trip
+                } else {
+                    popNext();
+                }
                 }
             }
             inNode = __ballot_sync(FULL, state == S_NODE);
@@ -214,6 +222,14 @@ TraverseBinaryKernel(DeviceScene sc, const float *__restrict__ rays, int n, b200
                 if (left == 0) left = __float_as_int(b.w);  // leaf header: count in the first slot
                 if (INST && __float_as_uint(b.y) == kInstanceTag) {
                     const InstanceDev *in = sc.instances + __float_as_int(b.z);
+                    {
+                        int2 c0, c1, c2, c3;
+                        RaySave(r, c0, c1, c2, c3);
+                        push(c0.x, c0.y);
+                        push(c1.x, c1.y);
+                        push(c2.x, c2.y);
+                        push(c3.x, c3.y);
+                    }
                     push(left - 1, __float_as_int(tMax));
                     push(kReturn | (slot + 1), 0);
                     const float4 *mi = reinterpret_cast<const float4 *>(in->mInv);
@@ -750,7 +766,7 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
                                   const int *nDev, int *exactScratch) {
     if (n <= 0) return cudaSuccess;
     if (n > 0x7fffffffll) return cudaErrorInvalidValue;
-    if (stackDepth > kSmemDepth + kLocalDepth) return cudaErrorInvalidValue;
+    if (stackDepth + 4 > kSmemDepth + kLocalDepth) return cudaErrorInvalidValue;  // + the saved parent context of an instance
     const bool wide = exactScratch && sc.wide && int(sc.maxStackWide) + 2 <= kSmemDepth + kLocalDepth;
     TraverseLaunch a{&sc, rays, n, hits, occluded, rayCounter, counters, smCount, refillMin, nodeMin, stream, nDev, nullptr,
                      exactScratch};

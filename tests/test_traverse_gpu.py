@@ -204,10 +204,43 @@ def test_config2_full_size_bit_exact_vs_reference(P, refrun):
     adv = P.scenes.adversarial_rays(sc, 1 << 20, seed=300)
     ref, _ = rs.closest(adv)
     mine = agg.IntersectClosest(adv, counters=True)
-    assert agg.trace_stats()["exact_rays"] > 0  # the axis-aligned ones took the exact binary walk
+    ts = agg.trace_stats()
+    assert ts["wide_nodes_visited"] == 0 or ts["exact_rays"] > 0  # wide walk: the axis-aligned rays took the exact binary walk
     assert hit_mismatches(mine, ref).sum() == 0
     occ_ref, _ = rs.any(adv)
     assert (agg.IntersectShadow(adv) != occ_ref).sum() == 0
     total += 2 * len(adv)
     assert total >= (1 << 25) + (1 << 21)
+    agg.close()
+
+
+@pytest.mark.parametrize("walk", ["wide", "binary"])
+def test_both_walks_match_reference(P, refrun, monkeypatch, walk):
+    """The two production walks - the exact binary pair-node walk (default) and the 8-wide walk with its conservative
+    child test + exact leaf-box test (B200PT_TRAVERSAL=wide) - each against the goldens, and on an instanced scene and a
+    200 K soup against the compiled reference, adversarial batches included; the wide walk must actually have run
+    (wide nodes counted) and must have handed its irregular rays to the binary walk."""
+    monkeypatch.setenv("B200PT_TRAVERSAL", walk)
+    for name in NAMES:
+        sc, rays = G.cases(P.scenes)[name]
+        gold = G.load(name)
+        agg = P.B200Aggregate(sc)
+        hits = agg.IntersectClosest(rays, counters=True)
+        ts = agg.trace_stats()
+        assert (ts["wide_nodes_visited"] > 0) == (walk == "wide")
+        if walk == "wide" and "adversarial" in name:
+            assert ts["exact_rays"] > 0
+        assert hit_mismatches(hits, gold["hits"], sc).sum() == 0
+        assert np.array_equal(agg.IntersectShadow(rays), gold["occ"])
+        agg.close()
+    sc = P.scenes.instanced_scene(n_objects=6, tris_per_object=15000, n_instances=150, world_tris=40000, seed=191)
+    rs = refrun.RefScene(sc)
+    agg = P.B200Aggregate(sc)
+    for rays in (P.scenes.primary_rays(1 << 18, seed=13), P.scenes.adversarial_rays(P.scenes.flattened(sc), 1 << 16, seed=14)):
+        ref, _ = rs.closest(rays)
+        mine = agg.IntersectClosest(rays)
+        assert hit_mismatches(mine, ref).sum() == 0
+        sh = P.scenes.shadow_rays(rays, mine)
+        occ, _ = rs.any(sh)
+        assert (agg.IntersectShadow(sh) != occ).sum() == 0
     agg.close()

@@ -15,8 +15,11 @@ def _on_device(torch, a):
     return torch.from_numpy(a.view(np.uint8).reshape(-1).copy()).cuda()
 
 
-def test_noalloc_entry_matches_intersect_closest(P):
+@pytest.mark.parametrize("walk", ["binary", "wide"])
+def test_noalloc_entry_matches_intersect_closest(P, monkeypatch, walk):
+    """walk = wide: the 8-wide walk, which hands its irregular rays to the binary walk through the scratch list."""
     import torch
+    monkeypatch.setenv("B200PT_TRAVERSAL", walk)
     capi = P.capi
     sc = P.scenes.random_soup(30000, seed=123)
     agg = P.B200Aggregate(sc, device=0)
