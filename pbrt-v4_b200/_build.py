@@ -29,7 +29,12 @@ CU_SOURCES = [
     ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=3"], "traverse_persist_3"),
     ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=4"], "traverse_persist_4"),
     ("traverse_persist.cu", ["--fmad=false", "-DB2_TP_PART=5"], "traverse_persist_5"),
-    ("render.cu", ["--fmad=false"]),
+    # one family of render kernels per part (see render.cu), built in parallel
+    ("render.cu", ["--fmad=false", "-DB2_RENDER_PART=0"], "render_0"),
+    ("render.cu", ["--fmad=false", "-DB2_RENDER_PART=1"], "render_1"),
+    ("render.cu", ["--fmad=false", "-DB2_RENDER_PART=2"], "render_2"),
+    ("render.cu", ["--fmad=false", "-DB2_RENDER_PART=3"], "render_3"),
+    ("render.cu", ["--fmad=false", "-DB2_RENDER_PART=4", "-DB2_SPECTRAL_UNROLL=4", "-DB2_VOL_MIN_BLOCKS=4"], "render_4"),
     ("noalloc.cu", []),
 ]
 
@@ -69,13 +74,14 @@ def build(verbose=False, force=False):
         f, extra = entry[0], entry[1]
         src, obj = os.path.join(CSRC, f), os.path.join(OBJ, (entry[2] if len(entry) > 2 else f) + ".o")
         objs.append(obj)
-        if force or _newer(src, obj, headers):
+        only = os.environ.get("B200PT_BUILD_ONLY")  # rebuild just these objects (comma separated), e.g. render_4
+        if (only and os.path.basename(obj)[:-2] in only.split(",")) or (not only and (force or _newer(src, obj, headers))):
             jobs.append([NVCC, "-std=c++17", "-O3", "-lineinfo", "-Xptxas", "-v", "-Xcompiler", "-fPIC",
                          "-Xcompiler", "-ffp-contract=off"] + GENCODE + extra + os.environ.get("B200PT_NVCC_EXTRA", "").split() + ["-c", src, "-o", obj])
     if jobs:
         with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
             list(ex.map(lambda c: _run(c, verbose), jobs))
-    if force or any(_newer(o, LIB, []) for o in objs):
+    if force or jobs or any(_newer(o, LIB, []) for o in objs):
         _run([NVCC, "-shared", "-o", LIB] + objs + GENCODE + ["-cudart", "static"], verbose)
     return LIB
 

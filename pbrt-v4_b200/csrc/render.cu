@@ -22,11 +22,19 @@ constexpr int kShadeBlock = 128;
 
 static size_t Al(size_t b) { return (b + 255) & ~size_t(255); }
 
+// The translation unit is compiled once per part (-DB2_RENDER_PART=k, pbrt-v4_b200/_build.py) so that the heavy template
+// kernels build in parallel: part 0 = everything but the kernels below + the diffuse shade kernels, parts 1-3 = the
+// conductor / dielectric / coated-diffuse shade kernels, part 4 = the volume-walk kernels.
+#ifndef B2_RENDER_PART
+#error "compile with -DB2_RENDER_PART=0..4"
+#endif
+
+#if B2_RENDER_PART == 0
 size_t PassBufferBytes(long long n, int depthSlots, bool vol) {
     size_t t = 0;
     if (vol)
         t += 5 * Al(sizeof(float) * kNLambda * n) + Al(sizeof(uint32_t) * kShadowAuxWords * n) +
-             Al(sizeof(uint32_t) * 6 * n) + Al(sizeof(int));
+             Al(sizeof(uint32_t) * 6 * n) + Al(2 * sizeof(int));
     t += 2 * Al(sizeof(float) * kNLambda * n);         // beta, L
     t += Al(sizeof(float) * kPathScalars * n);
     t += Al(sizeof(int) * kPathInts * n);
@@ -73,9 +81,11 @@ void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuf
         pb.shRu = (float *)take(sizeof(float) * kNLambda * n);
         pb.shAux = (uint32_t *)take(sizeof(uint32_t) * kShadowAuxWords * n);
         pb.shHits = (uint32_t *)take(sizeof(uint32_t) * 6 * n);
-        pb.shContinue = (int *)take(sizeof(int));
+        pb.shContinue = (int *)take(2 * sizeof(int));  // [0] walks that go on, [1] work cursor of the persistent walk kernels
     }
 }
+
+#endif  // part 0
 
 // ---- queue push: one atomic per group of converged lanes
 __device__ __forceinline__ int QueuePush(int *counter) {
@@ -218,6 +228,7 @@ struct MediumIO {
     }
 };
 
+#if B2_RENDER_PART == 0
 // ---- camera rays: RayIntegrator::EvaluatePixelSample up to GenerateRay (cpu/integrators.cpp:228-262)
 __global__ void __launch_bounds__(kShadeBlock)
 GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nActive, int firstSample,
@@ -283,6 +294,8 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
         if (type == m) pb.matQ[m][QueuePush(counts + 2 + m)] = t;
 }
 
+#endif  // part 0
+
 #ifndef B2_SHADE_MIN_BLOCKS
 #define B2_SHADE_MIN_BLOCKS 4  // 128 registers: the layered walks are latency bound, four blocks per SM beat three
 #endif
@@ -330,6 +343,7 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     }
 }
 
+#if B2_RENDER_PART == 4
 // ---- volpath: the rays of this iteration that travel in a medium (cpu/integrators.cpp:968-1075).  Absorbed and
 // scattered paths are finished here (their hit slot is marked consumed); survivors go on to classify / shade
 // with beta, r_u, r_l rescaled.
@@ -363,123 +377,236 @@ VolSortKernel(RenderSceneDev rs, PassBuffers pb, int depth, int mode) {
 #ifndef B2_VOL_MIN_BLOCKS
 #define B2_VOL_MIN_BLOCKS 3
 #endif
+// The two walk kernels are PERSISTENT with lane refill: a thread takes rays off the work lists until they are used up,
+// and the warp executes one common body per round - one step of the delta / ratio-tracking walk (TMajWalk::Step) for
+// every lane that is walking.  Walk lengths differ by orders of magnitude between rays (vacuum, thin fog, the dense
+// grid): with one ray per thread a warp waited for its longest walk at ~6 active lanes (profiles/r01_config5_*).
+// Starting a ray (header, spectra, DDA set-up) and finishing one (light / phase sampling, stores) are long divergent
+// blocks, so they are batched too: lanes wait until kVolBatch of them are ready (or nobody is walking).
+constexpr int kVolBatch = 8;
+enum : int { W_IDLE = 0, W_WALK = 1, W_END = 2, W_OUT = 3, W_COLLIDE = 4 };
+constexpr int kVolCellsPerRound = 4;  // majorant segments a walking lane may cross per round
+
+// takes `nIdle` consecutive items off the cursor for the idle lanes; -1 = the lists are used up
+__device__ __forceinline__ int VolFetch(int *cursor, unsigned idleMask, bool idle, int total) {
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == __ffs(idleMask) - 1) base = atomicAdd(cursor, __popc(idleMask));
+    base = __shfl_sync(0xffffffffu, base, __ffs(idleMask) - 1);
+    if (!idle) return -1;
+    int qi = base + __popc(idleMask & ((1u << lane) - 1));
+    return qi < total ? qi : -1;
+}
+
 template <int LBVH, int EXT>
 __global__ void __launch_bounds__(kShadeBlock, B2_VOL_MIN_BLOCKS)
-VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width, int kind) {
-    int qi = blockIdx.x * blockDim.x + threadIdx.x;
+VolMediumKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width, int *cursor) {
     int *counts = pb.counts + kCountStride * depth;
-    if (qi >= counts[6 + kind]) return;
-    const int t = pb.matQ[kind][qi];
+    const int n0 = counts[6], total = n0 + counts[7];  // homogeneous media first, then grids (VolSortKernel)
     const int cur = depth & 1, nxt = cur ^ 1;
     const long long n = pb.n;
-    int path = pb.rayPath[cur][t];
-    const float *r = pb.rays[cur] + 7ll * t;
-    PathRegs p;
-    LoadHeader(pb, path, p);
-    int pix = path % nPixels;
-    p.px = rs.film.x0 + pix % width;
-    p.py = rs.film.y0 + pix / width;
-    p.rayO = mk(r[0], r[1], r[2]);
-    p.rayD = mk(r[3], r[4], r[5]);
-    p.rayTMax = r[6];
-    uint32_t slot = pb.hits[6ll * t];
-    float tHit = slot == kMissTag ? INFINITY : __uint_as_float(pb.hits[6ll * t + 1]);
     __shared__ float sstate[3 * kNLambda * kShadeBlock];
     float *mine = sstate + threadIdx.x;
+    const unsigned FULL = 0xffffffffu;
+    int state = W_IDLE, t = 0, path = 0;
+    bool exhausted = false;
+    PathRegs p;
+    VolMediumState st;
+    TMajFastWalk fw;
+    bool tail = false;
+    while (true) {
+        const unsigned mAdv = __ballot_sync(FULL, state == W_WALK), mColl = __ballot_sync(FULL, state == W_COLLIDE);
+        const unsigned mWalk = mAdv | mColl;
+        unsigned mEnd = __ballot_sync(FULL, state == W_END);
+        if (mEnd && (__popc(mEnd) >= kVolBatch || !mWalk)) {
+            if (state == W_END) {
+                MediumIO io(pb, path, counts + 1, mine);
+                if (tail) fw.TMaj(st.sigT, st.T_maj);
+                tail = false;
+                int res = VolMediumEnd<MediumIO, LBVH, EXT>(rs, p, st, io);
+                if (res != VOL_TERMINATED) {
 #pragma unroll 8
-    for (int k = 0; k < kNLambda; ++k) {
-        mine[k * kShadeBlock] = pb.beta[k * n + path];
-        mine[(kNLambda + k) * kShadeBlock] = pb.ru[k * n + path];
-        mine[(2 * kNLambda + k) * kShadeBlock] = pb.rl[k * n + path];
-    }
-    MediumIO io(pb, path, counts + 1, mine);
-    int res = VolMediumStep<MediumIO, LBVH, EXT>(rs, p, tHit, io);
-    if (res != VOL_TERMINATED) {
+                    for (int k = 0; k < kNLambda; ++k) {
+                        pb.beta[k * n + path] = mine[k * kShadeBlock];
+                        pb.ru[k * n + path] = mine[(kNLambda + k) * kShadeBlock];
+                        pb.rl[k * n + path] = mine[(2 * kNLambda + k) * kShadeBlock];
+                    }
+                }
+                if (res == VOL_SURVIVE) {
+                    StoreHeader(pb, path, p);
+                } else {
+                    pb.hits[6ll * t] = kConsumedTag;
+                    if (res == VOL_TERMINATED) {
+                        pb.ints[3 * n + path] = (int)(p.flags & ~PF_ALIVE);
+                    } else {
+                        int *next = pb.counts + kCountStride * (depth + 1);
+                        int ns = QueuePush(next);
+                        StoreRay(pb.rays[nxt], ns, p.rayO, p.rayD, p.rayTMax);
+                        pb.rayPath[nxt][ns] = path;
+                        StoreHeader(pb, path, p);
+                    }
+                }
+                state = W_IDLE;
+            }
+        }
+        unsigned mIdle = __ballot_sync(FULL, state == W_IDLE);
+        if (mIdle && !exhausted && (__popc(mIdle) >= kVolBatch || !mWalk)) {
+            int qi = VolFetch(cursor, mIdle, state == W_IDLE, total);
+            if (state == W_IDLE) {
+                if (qi < 0) {
+                    state = W_OUT;
+                } else {
+                    t = qi < n0 ? pb.matQ[0][qi] : pb.matQ[1][qi - n0];
+                    path = pb.rayPath[cur][t];
+                    const float *r = pb.rays[cur] + 7ll * t;
+                    LoadHeader(pb, path, p);
+                    int pix = path % nPixels;
+                    p.px = rs.film.x0 + pix % width;
+                    p.py = rs.film.y0 + pix / width;
+                    p.rayO = mk(r[0], r[1], r[2]);
+                    p.rayD = mk(r[3], r[4], r[5]);
+                    p.rayTMax = r[6];
+                    uint32_t slot = pb.hits[6ll * t];
+                    float tHit = slot == kMissTag ? INFINITY : __uint_as_float(pb.hits[6ll * t + 1]);
 #pragma unroll 8
-        for (int k = 0; k < kNLambda; ++k) {
-            pb.beta[k * n + path] = mine[k * kShadeBlock];
-            pb.ru[k * n + path] = mine[(kNLambda + k) * kShadeBlock];
-            pb.rl[k * n + path] = mine[(2 * kNLambda + k) * kShadeBlock];
+                    for (int k = 0; k < kNLambda; ++k) {
+                        mine[k * kShadeBlock] = pb.beta[k * n + path];
+                        mine[(kNLambda + k) * kShadeBlock] = pb.ru[k * n + path];
+                        mine[(2 * kNLambda + k) * kShadeBlock] = pb.rl[k * n + path];
+                    }
+                    VolMediumBeginFast(rs, p, tHit, st, fw);
+                    state = W_WALK;
+                }
+            }
+            if (__any_sync(FULL, state == W_OUT)) exhausted = true;
+        }
+        if (!__any_sync(FULL, state == W_WALK || state == W_COLLIDE || state == W_END || (state == W_IDLE && !exhausted))) break;
+        // the pending tentative collisions once enough lanes have one (or nobody is left to advance), else the scalar walk
+        if (mColl && (__popc(mColl) >= kVolBatch || !mAdv)) {
+            if (state == W_COLLIDE) {
+                MediumIO io(pb, path, counts + 1, mine);
+                state = VolMediumCollide(rs, p, st, fw, io) ? W_WALK : W_END;
+            }
+        } else if (state == W_WALK) {
+            int r = fw.Advance(rs.media[p.medium], st.sigT[0], st.rng, kVolCellsPerRound);
+            if (r == TMAJ_COLLISION) {
+                state = W_COLLIDE;
+            } else if (r == TMAJ_RAN_OUT) {
+                tail = true;  // T_maj of the stretch after the last collision: formed with the batch in W_END
+                state = W_END;
+            }
         }
     }
-    if (res == VOL_SURVIVE) {
-        StoreHeader(pb, path, p);
-        return;
-    }
-    pb.hits[6ll * t] = kConsumedTag;
-    if (res == VOL_TERMINATED) {
-        pb.ints[3 * n + path] = (int)(p.flags & ~PF_ALIVE);
-        return;
-    }
-    int *next = pb.counts + kCountStride * (depth + 1);
-    int ns = QueuePush(next);
-    StoreRay(pb.rays[nxt], ns, p.rayO, p.rayD, p.rayTMax);
-    pb.rayPath[nxt][ns] = path;
-    StoreHeader(pb, path, p);
 }
 
 // ---- volpath: one segment of every light sample's transmittance walk (cpu/integrators.cpp:1334-1395).  pb.shHits
 // holds the closest hits of the shadow rays.  A walk that reaches the light adds its estimate to the path's
 // radiance; one that meets an interface leaves its next ray in the same slot and counts in pb.shContinue.
+// Work lists: walks outside any medium, in a homogeneous medium, in a grid (counts[2..4], VolSortKernel).
 template <int EXT>
 __global__ void __launch_bounds__(kShadeBlock, B2_VOL_MIN_BLOCKS)
-ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth, int kind) {
-    int qi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (qi >= pb.counts[kCountStride * depth + 2 + kind]) return;
-    const int t = pb.matQ[kind][qi];
-    int path = pb.shPath[t];
+ShadowTrKernel(RenderSceneDev rs, PassBuffers pb, int depth, int *cursor) {
+    const int *counts = pb.counts + kCountStride * depth;
+    const int n0 = counts[2], n1 = n0 + counts[3], total = n1 + counts[4];
     const long long n = pb.n;
-    float *ray = pb.shRays + 7ll * t;
-    uint32_t *a = pb.shAux + (long long)kShadowAuxWords * t;
+    const unsigned FULL = 0xffffffffu;
+    int state = W_IDLE, t = 0, path = 0, res = -1;
+    bool exhausted = false;
     ShadowRegs sh;
-    sh.o = mk(ray[0], ray[1], ray[2]);
-    sh.d = mk(ray[3], ray[4], ray[5]);
-    sh.medium = (int)a[2];
-    sh.lightPi.lo = mk(__uint_as_float(a[8]), __uint_as_float(a[9]), __uint_as_float(a[10]));
-    sh.lightPi.hi = mk(__uint_as_float(a[11]), __uint_as_float(a[12]), __uint_as_float(a[13]));
-    sh.lightN = mk(__uint_as_float(a[14]), __uint_as_float(a[15]), __uint_as_float(a[16]));
+    ShadowTrState st;
+    TMajFastWalk fw;
+    bool tail = false;
     float T[kNLambda], rl[kNLambda], ru[kNLambda];
-    const bool started = a[3] != 0;
-    if (started) {
-        sh.rng.state = (uint64_t)a[4] | ((uint64_t)a[5] << 32);
-        sh.rng.inc = (uint64_t)a[6] | ((uint64_t)a[7] << 32);
-        for (int k = 0; k < kNLambda; ++k) {
-            T[k] = pb.shT[k * n + t];
-            rl[k] = pb.shRl[k * n + t];
-            ru[k] = pb.shRu[k * n + t];
+    while (true) {
+        const unsigned mAdv = __ballot_sync(FULL, state == W_WALK), mColl = __ballot_sync(FULL, state == W_COLLIDE);
+        const unsigned mWalk = mAdv | mColl;
+        unsigned mEnd = __ballot_sync(FULL, state == W_END);
+        if (mEnd && (__popc(mEnd) >= kVolBatch || !mWalk)) {
+            if (state == W_END) {
+                float *ray = pb.shRays + 7ll * t;
+                uint32_t *a = pb.shAux + (long long)kShadowAuxWords * t;
+                if (tail) fw.TMaj(st.sigT, st.T_maj);
+                tail = false;
+                if (res < 0) res = ShadowTrEnd(rs, sh, st, T, rl, ru);
+                if (res == SHADOW_CONTINUE) {
+                    StoreRay(pb.shRays, t, sh.o, sh.d, ray[6]);
+                    a[2] = (uint32_t)sh.medium;
+                    a[3] = 1;
+                    a[4] = (uint32_t)sh.rng.state; a[5] = (uint32_t)(sh.rng.state >> 32);
+                    a[6] = (uint32_t)sh.rng.inc;   a[7] = (uint32_t)(sh.rng.inc >> 32);
+                    for (int k = 0; k < kNLambda; ++k) {
+                        pb.shT[k * n + t] = T[k];
+                        pb.shRl[k * n + t] = rl[k];
+                        pb.shRu[k * n + t] = ru[k];
+                    }
+                    atomicAdd(pb.shContinue, 1);
+                } else {
+                    if (res == SHADOW_REACHED)
+                        ShadowTrFinish(T, rl, ru, __uint_as_float(a[0]), __uint_as_float(a[1]),
+                                       [&](int k) { return pb.Ld[k * n + t]; }, [&](int k) { return pb.ru[k * n + path]; },
+                                       [&](int k, float v) { pb.L[k * n + path] += v; });
+                    pb.shPath[t] = -1;
+                    ray[6] = -1.f;
+                }
+                state = W_IDLE;
+            }
         }
-    } else {
-        sh.rng = PcgSeed(Hash3f(sh.o.x, sh.o.y, sh.o.z), Hash3f(sh.d.x, sh.d.y, sh.d.z));
-        for (int k = 0; k < kNLambda; ++k) T[k] = rl[k] = ru[k] = 1.f;
-    }
-    uint32_t hit[6];
-    for (int i = 0; i < 6; ++i) hit[i] = pb.shHits[6ll * t + i];
-    int res = ShadowTrSegment<EXT>(rs, pb.scalars[path], sh, hit, T, rl, ru);
-    if (res == SHADOW_CONTINUE) {
-        StoreRay(pb.shRays, t, sh.o, sh.d, ray[6]);
-        a[2] = (uint32_t)sh.medium;
-        a[3] = 1;
-        a[4] = (uint32_t)sh.rng.state; a[5] = (uint32_t)(sh.rng.state >> 32);
-        a[6] = (uint32_t)sh.rng.inc;   a[7] = (uint32_t)(sh.rng.inc >> 32);
-        for (int k = 0; k < kNLambda; ++k) {
-            pb.shT[k * n + t] = T[k];
-            pb.shRl[k * n + t] = rl[k];
-            pb.shRu[k * n + t] = ru[k];
+        unsigned mIdle = __ballot_sync(FULL, state == W_IDLE);
+        if (mIdle && !exhausted && (__popc(mIdle) >= kVolBatch || !mWalk)) {
+            int qi = VolFetch(cursor, mIdle, state == W_IDLE, total);
+            if (state == W_IDLE) {
+                if (qi < 0) {
+                    state = W_OUT;
+                } else {
+                    t = qi < n0 ? pb.matQ[0][qi] : (qi < n1 ? pb.matQ[1][qi - n0] : pb.matQ[2][qi - n1]);
+                    path = pb.shPath[t];
+                    const float *ray = pb.shRays + 7ll * t;
+                    const uint32_t *a = pb.shAux + (long long)kShadowAuxWords * t;
+                    sh.o = mk(ray[0], ray[1], ray[2]);
+                    sh.d = mk(ray[3], ray[4], ray[5]);
+                    sh.medium = (int)a[2];
+                    sh.lightPi.lo = mk(__uint_as_float(a[8]), __uint_as_float(a[9]), __uint_as_float(a[10]));
+                    sh.lightPi.hi = mk(__uint_as_float(a[11]), __uint_as_float(a[12]), __uint_as_float(a[13]));
+                    sh.lightN = mk(__uint_as_float(a[14]), __uint_as_float(a[15]), __uint_as_float(a[16]));
+                    if (a[3] != 0) {  // the walk goes on from an earlier segment
+                        sh.rng.state = (uint64_t)a[4] | ((uint64_t)a[5] << 32);
+                        sh.rng.inc = (uint64_t)a[6] | ((uint64_t)a[7] << 32);
+                        for (int k = 0; k < kNLambda; ++k) {
+                            T[k] = pb.shT[k * n + t];
+                            rl[k] = pb.shRl[k * n + t];
+                            ru[k] = pb.shRu[k * n + t];
+                        }
+                    } else {
+                        sh.rng = PcgSeed(Hash3f(sh.o.x, sh.o.y, sh.o.z), Hash3f(sh.d.x, sh.d.y, sh.d.z));
+                        for (int k = 0; k < kNLambda; ++k) T[k] = rl[k] = ru[k] = 1.f;
+                    }
+                    uint32_t hit[6];
+                    for (int i = 0; i < 6; ++i) hit[i] = pb.shHits[6ll * t + i];
+                    res = ShadowTrBeginFast<EXT>(rs, pb.scalars[path], sh, hit, st, fw);
+                    state = (res < 0 && st.walking) ? W_WALK : W_END;
+                }
+            }
+            if (__any_sync(FULL, state == W_OUT)) exhausted = true;
         }
-        atomicAdd(pb.shContinue, 1);
-        return;
+        if (!__any_sync(FULL, state == W_WALK || state == W_COLLIDE || state == W_END || (state == W_IDLE && !exhausted))) break;
+        if (mColl && (__popc(mColl) >= kVolBatch || !mAdv)) {
+            if (state == W_COLLIDE) state = ShadowTrCollide(rs, sh, st, fw, T, rl, ru) ? W_WALK : W_END;
+        } else if (state == W_WALK) {
+            int r = fw.Advance(rs.media[sh.medium], st.sigT[0], sh.rng, kVolCellsPerRound);
+            if (r == TMAJ_COLLISION) {
+                state = W_COLLIDE;
+            } else if (r == TMAJ_RAN_OUT) {
+                tail = true;
+                state = W_END;
+            }
+        }
     }
-    if (res == SHADOW_REACHED)
-        ShadowTrFinish(T, rl, ru, __uint_as_float(a[0]), __uint_as_float(a[1]), [&](int k) { return pb.Ld[k * n + t]; },
-                       [&](int k) { return pb.ru[k * n + path]; }, [&](int k, float v) { pb.L[k * n + path] += v; });
-    pb.shPath[t] = -1;
-    ray[6] = -1.f;
 }
 
-}  // namespace b200pt
-#include "render_volume_warp.cuh"
-namespace b200pt {
 
+#endif  // part 4
+
+#if B2_RENDER_PART == 0
 // ---- unoccluded light samples join the path's radiance (RecordShadowRayResult, wavefront/intersect.h:176-190)
 __global__ void __launch_bounds__(256)
 ResolveShadowKernel(PassBuffers pb, int depth) {
@@ -581,8 +708,11 @@ __global__ void SumCountsKernel(PassBuffers pb, int depths, unsigned long long *
     totals[1] += s;
 }
 
+#endif  // part 0
+
 static inline int Blocks(long long n, int b) { return (int)((n + b - 1) / b); }
 
+#if B2_RENDER_PART == 0
 cudaError_t LaunchGenerate(const RenderSceneDev &rs, const PassBuffers &pb, int nPixels, int width, int nActive,
                            int firstSample, int sampleStride, cudaStream_t stream) {
     GenerateKernel<<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, nPixels, width, nActive,
@@ -594,85 +724,107 @@ cudaError_t LaunchClassify(const RenderSceneDev &rs, const PassBuffers &pb, int 
     ClassifyKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth);
     return cudaGetLastError();
 }
+#endif  // part 0
+
+// one material's shade kernels per part
+#define B2_SHADE_MAT_FN(NAME, MAT)                                                                       \
+    cudaError_t NAME(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width,  \
+                     int nActive, cudaStream_t stream) {                                                  \
+        const int grid = Blocks(nActive, kShadeBlock);                                                    \
+        const bool lbvh = rs.integrator.lightSampler == 2, vol = rs.integrator.type == 1;                 \
+        const bool ext = rs.geomExt != 0; /* patches / per-vertex normals or uv somewhere in the scene */ \
+        if (vol && lbvh) {                                                                                \
+            if (ext) ShadeKernel<MAT, 1, 1, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
+            else ShadeKernel<MAT, 1, 1, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);     \
+        } else if (vol) {                                                                                 \
+            if (ext) ShadeKernel<MAT, 0, 1, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
+            else ShadeKernel<MAT, 0, 1, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);     \
+        } else if (lbvh) {                                                                                \
+            if (ext) ShadeKernel<MAT, 1, 0, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
+            else ShadeKernel<MAT, 1, 0, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);     \
+        } else {                                                                                          \
+            if (ext) ShadeKernel<MAT, 0, 0, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
+            else ShadeKernel<MAT, 0, 0, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width);     \
+        }                                                                                                 \
+        return cudaGetLastError();                                                                        \
+    }
+cudaError_t LaunchShadeDiffuse(const RenderSceneDev &, const PassBuffers &, int, int, int, int, cudaStream_t);
+cudaError_t LaunchShadeConductor(const RenderSceneDev &, const PassBuffers &, int, int, int, int, cudaStream_t);
+cudaError_t LaunchShadeDielectric(const RenderSceneDev &, const PassBuffers &, int, int, int, int, cudaStream_t);
+cudaError_t LaunchShadeCoated(const RenderSceneDev &, const PassBuffers &, int, int, int, int, cudaStream_t);
+#if B2_RENDER_PART == 0
+B2_SHADE_MAT_FN(LaunchShadeDiffuse, MAT_DIFFUSE)
 cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width,
                         int nActive, uint32_t matMask, cudaStream_t stream, int *launches) {
-    int grid = Blocks(nActive, kShadeBlock);
-    const bool lbvh = rs.integrator.lightSampler == 2, vol = rs.integrator.type == 1;
-    const bool ext = rs.geomExt != 0;  // patches / per-vertex normals or uv somewhere in the scene
-#define B2_SHADE_EXT(MAT, L, V)                                                                         \
-    do {                                                                                                \
-        if (ext)                                                                                        \
-            ShadeKernel<MAT, L, V, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
-        else                                                                                            \
-            ShadeKernel<MAT, L, V, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width); \
-    } while (0)
-#define B2_SHADE(bit, MAT)                                                                              \
-    if (matMask & (bit)) {                                                                              \
-        if (vol && lbvh)                                                                                \
-            B2_SHADE_EXT(MAT, 1, 1);                                                                    \
-        else if (vol)                                                                                   \
-            B2_SHADE_EXT(MAT, 0, 1);                                                                    \
-        else if (lbvh)                                                                                  \
-            B2_SHADE_EXT(MAT, 1, 0);                                                                    \
-        else                                                                                            \
-            B2_SHADE_EXT(MAT, 0, 0);                                                                    \
-        ++*launches;                                                                                    \
-    }
-    B2_SHADE(1u, MAT_DIFFUSE)
-    B2_SHADE(2u, MAT_CONDUCTOR)
-    B2_SHADE(4u, MAT_DIELECTRIC)
-    B2_SHADE(8u, MAT_COATED_DIFFUSE)
-#undef B2_SHADE
-#undef B2_SHADE_EXT
-    return cudaGetLastError();
+    cudaError_t e = cudaSuccess;
+    if ((matMask & 1u) && e == cudaSuccess) e = (++*launches, LaunchShadeDiffuse(rs, pb, depth, nPixels, width, nActive, stream));
+    if ((matMask & 2u) && e == cudaSuccess) e = (++*launches, LaunchShadeConductor(rs, pb, depth, nPixels, width, nActive, stream));
+    if ((matMask & 4u) && e == cudaSuccess) e = (++*launches, LaunchShadeDielectric(rs, pb, depth, nPixels, width, nActive, stream));
+    if ((matMask & 8u) && e == cudaSuccess) e = (++*launches, LaunchShadeCoated(rs, pb, depth, nPixels, width, nActive, stream));
+    return e;
 }
-constexpr int kVolWarpGrid = 148 * 16;  // persistent-style grid of the warp-per-ray kernels (stride loop over the list)
+#elif B2_RENDER_PART == 1
+B2_SHADE_MAT_FN(LaunchShadeConductor, MAT_CONDUCTOR)
+#elif B2_RENDER_PART == 2
+B2_SHADE_MAT_FN(LaunchShadeDielectric, MAT_DIELECTRIC)
+#elif B2_RENDER_PART == 3
+B2_SHADE_MAT_FN(LaunchShadeCoated, MAT_COATED_DIFFUSE)
+#endif
+#undef B2_SHADE_MAT_FN
+
+#if B2_RENDER_PART == 4
+// resident blocks of the persistent walk kernels: SMs x B2_VOL_MIN_BLOCKS
+static int VolPersistGrid() {
+    static int g = 0;
+    if (!g) {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        g = sms * B2_VOL_MIN_BLOCKS;
+    }
+    return g;
+}  // persistent-style grid of the warp-per-ray kernels (stride loop over the list)
 
 cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width, int nActive,
-                            cudaStream_t stream, bool warpPerRay) {
-    int grid = Blocks(nActive, kShadeBlock);
+                            cudaStream_t stream) {
     VolSortKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth, 0);
-    for (int kind = 0; kind < 2 && warpPerRay; ++kind) {
-        int g = (int)std::min<long long>(kVolWarpGrid, Blocks(nActive, kVolWarpBlock / 32));
-        if (rs.integrator.lightSampler == 2)
-            VolMediumWarpKernel<1><<<g, kVolWarpBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
+    // persistent: the resident set of blocks works the two lists off a cursor
+    int *cursor = pb.shContinue + 1;
+    cudaError_t e = cudaMemsetAsync(cursor, 0, sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    const int g = (int)std::min<long long>(Blocks(nActive, kShadeBlock), (long long)VolPersistGrid());
+    const bool lb = rs.integrator.lightSampler == 2;
+    if (rs.geomExt) {
+        if (lb)
+            VolMediumKernel<1, 1><<<g, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, cursor);
         else
-            VolMediumWarpKernel<0><<<g, kVolWarpBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
-    }
-    for (int kind = 0; kind < 2 && !warpPerRay; ++kind) {
-        const bool lb = rs.integrator.lightSampler == 2;
-        if (rs.geomExt) {
-            if (lb)
-                VolMediumKernel<1, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
-            else
-                VolMediumKernel<0, 1><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
-        } else {
-            if (lb)
-                VolMediumKernel<1, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
-            else
-                VolMediumKernel<0, 0><<<grid, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, kind);
-        }
+            VolMediumKernel<0, 1><<<g, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, cursor);
+    } else {
+        if (lb)
+            VolMediumKernel<1, 0><<<g, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, cursor);
+        else
+            VolMediumKernel<0, 0><<<g, kShadeBlock, 0, stream>>>(rs, pb, depth, nPixels, width, cursor);
     }
     return cudaGetLastError();
 }
-cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream,
-                           bool warpPerRay) {
+cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {
     // counts[2..4] of this iteration: the material queues are spent, the slots hold the walk queues' lengths
     cudaError_t e = cudaMemsetAsync(pb.counts + kCountStride * depth + 2, 0, 3 * sizeof(int), stream);
     if (e != cudaSuccess) return e;
     VolSortKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(rs, pb, depth, 1);
-    for (int kind = 0; kind < 3; ++kind) {
-        // walks outside any medium (kind 0) only tell occluders from interfaces: a thread per ray is the better fit
-        if (warpPerRay && kind > 0)
-            ShadowTrWarpKernel<<<(int)std::min<long long>(kVolWarpGrid, Blocks(nActive, kVolWarpBlock / 32)), kVolWarpBlock, 0,
-                                 stream>>>(rs, pb, depth, kind);
-        else if (rs.geomExt)
-            ShadowTrKernel<1><<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
-        else
-            ShadowTrKernel<0><<<Blocks(nActive, kShadeBlock), kShadeBlock, 0, stream>>>(rs, pb, depth, kind);
-    }
+    int *cursor = pb.shContinue + 1;
+    e = cudaMemsetAsync(cursor, 0, sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    const int g = (int)std::min<long long>(Blocks(nActive, kShadeBlock), (long long)VolPersistGrid());
+    if (rs.geomExt)
+        ShadowTrKernel<1><<<g, kShadeBlock, 0, stream>>>(rs, pb, depth, cursor);
+    else
+        ShadowTrKernel<0><<<g, kShadeBlock, 0, stream>>>(rs, pb, depth, cursor);
     return cudaGetLastError();
 }
+#endif  // part 4
+
+#if B2_RENDER_PART == 0
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream) {
     ResolveShadowKernel<<<Blocks(nActive, 256), 256, 0, stream>>>(pb, depth);
     return cudaGetLastError();
@@ -704,5 +856,7 @@ cudaError_t LaunchSumCounts(const PassBuffers &pb, int depths, unsigned long lon
     SumCountsKernel<<<1, 1, 0, stream>>>(pb, depths, totals);
     return cudaGetLastError();
 }
+
+#endif  // part 0
 
 }  // namespace b200pt

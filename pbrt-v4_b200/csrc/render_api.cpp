@@ -36,8 +36,9 @@ struct b200pt_render {
     int *dRayCounter = nullptr;               // work counter of the persistent traversal kernel
     int nPixels = 0;
     size_t filmDoubles = 0;  // 4 per pixel, + 2 * nBuckets per pixel for a spectral film
-    long long maxPathsPerPass = 4ll << 20;    // B200PT_PASS_PATHS overrides
-    bool volWarp = false;                     // B200PT_VOL_KERNEL=warp: the warp-per-ray volume kernels (measured slower)
+    // paths per pass: up to 32 Mi when 40 % of the free device memory holds their buffers (fewer, longer launches; a
+    // 1920 x 1080 frame takes 16 samples per pixel per pass), never below 4 Mi; B200PT_PASS_PATHS overrides
+    long long maxPathsPerPass = 4ll << 20;
     b200pt_render_stats stats{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
@@ -140,8 +141,18 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     for (const MeshAttrDev &m : r->host.meshes)
         if (m.material < 0) r->matMask |= 1u;  // null materials go through the diffuse queue, which ends the path
     if (r->matMask == 0) r->matMask = 1;
+    {
+        size_t freeB = 0, totalB = 0;
+        if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
+            const bool volPath = r->dev.integrator.type == 1;
+            const size_t perPath = PassBufferBytes(1 << 20, volPath ? kVolMaxIterations + 2 : r->dev.integrator.maxDepth + 2, volPath) >> 20;
+            const long long fit = (long long)(0.4 * double(freeB) / double(std::max<size_t>(perPath, 1)));
+            r->maxPathsPerPass = std::max(4ll << 20, std::min(32ll << 20, fit));
+        } else {
+            (void)cudaGetLastError();
+        }
+    }
     if (const char *v = getenv("B200PT_PASS_PATHS")) r->maxPathsPerPass = std::max(1ll, atoll(v));
-    if (const char *v = getenv("B200PT_VOL_KERNEL")) r->volWarp = std::string(v) == "warp";
     r->filmDoubles = size_t(r->nPixels) * (4 + 2 * size_t(r->dev.film.nBuckets));
     if (cudaMalloc((void **)&r->dFilm, sizeof(double) * r->filmDoubles) != cudaSuccess ||
         cudaMalloc((void **)&r->dImage, sizeof(float) * std::max(3, r->dev.film.nBuckets) * size_t(r->nPixels)) != cudaSuccess ||
@@ -224,8 +235,8 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                                                    ctx->nodeMin, ctx->stream, true, nRays, exact));
                 ++launches;
                 if (r->dev.nMedia) {
-                    B2_CUDA(ctx, LaunchVolMedium(r->dev, pb, j, nPix, width, nActive, ctx->stream, r->volWarp));
-                    launches += 3;
+                    B2_CUDA(ctx, LaunchVolMedium(r->dev, pb, j, nPix, width, nActive, ctx->stream));
+                    launches += 2;
                 }
                 B2_CUDA(ctx, LaunchClassify(r->dev, pb, j, nActive, ctx->stream));
                 ++launches;
@@ -242,8 +253,8 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                     B2_CUDA(ctx, LaunchTraversePersist(sc, pb.shRays, hc[0], (b200pt_hit *)pb.shHits, nullptr, false,
                                                        r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
                                                        ctx->nodeMin, ctx->stream, true, nShadow, exact));
-                    B2_CUDA(ctx, LaunchShadowTr(r->dev, pb, j, hc[0], ctx->stream, r->volWarp));
-                    launches += 5;
+                    B2_CUDA(ctx, LaunchShadowTr(r->dev, pb, j, hc[0], ctx->stream));
+                    launches += 3;
                     B2_CUDA(ctx, cudaMemcpyAsync(&live, pb.shContinue, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
                     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
                 }

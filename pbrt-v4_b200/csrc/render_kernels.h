@@ -64,12 +64,9 @@ cudaError_t LaunchShade(const RenderSceneDev &rs, const PassBuffers &pb, int dep
                         int nActive, uint32_t matMask, cudaStream_t stream, int *launches);
 // volpath: delta tracking of the rays that travel in a medium (before classify), one segment of every light
 // sample's transmittance walk (after a closest-hit pass over the shadow rays into pb.shHits)
-// warpPerRay: one warp per ray, one lane per wavelength (render_volume_warp.cuh; B200PT_VOL_KERNEL=warp; measured
-// slower, kept as the alternative it was tested against); false = a thread per ray, the default
 cudaError_t LaunchVolMedium(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nPixels, int width, int nActive,
-                            cudaStream_t stream, bool warpPerRay);
-cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream,
-                           bool warpPerRay);
+                            cudaStream_t stream);
+cudaError_t LaunchShadowTr(const RenderSceneDev &rs, const PassBuffers &pb, int depth, int nActive, cudaStream_t stream);
 cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, cudaStream_t stream);
 cudaError_t LaunchFinish(const RenderSceneDev &rs, const PassBuffers &pb, int nActive, cudaStream_t stream);
 cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream);

@@ -25,8 +25,16 @@ enum : uint32_t {
     PF_TERMINATED_SECONDARY = 16u  // SampledWavelengths::TerminateSecondary happened (util/spectrum.h:346-353)
 };
 
+// the 31-trip spectral loops stay (mostly) rolled on the device: unrolled by B2_SPECTRAL_UNROLL (2: the shade kernels
+// are register bound; the volume-walk kernels, whose spectral state lives in local memory, take 8 so that the loads of
+// several wavelengths are in flight together - set per translation unit by the build)
+#ifndef B2_SPECTRAL_UNROLL
+#define B2_SPECTRAL_UNROLL 2
+#endif
+#define B2_PRAGMA_(x) _Pragma(#x)
+#define B2_PRAGMA(x) B2_PRAGMA_(x)
 #if defined(__CUDA_ARCH__)
-#define B2_SPECTRAL_LOOP _Pragma("unroll 2")
+#define B2_SPECTRAL_LOOP B2_PRAGMA(unroll B2_SPECTRAL_UNROLL)
 #else
 #define B2_SPECTRAL_LOOP
 #endif

@@ -95,19 +95,94 @@ enum { VOL_SURVIVE = 0, VOL_TERMINATED = 1, VOL_SCATTERED = 2 };
 
 // The `if (ray.medium)` block of VolPathIntegrator::Li for the ray p.ray with closest hit at tHit (INFINITY = none).
 // IO adds Ru/SetRu/Rl/SetRl (rescaled path probabilities) and ShadowEndVol to ShadeVertex's IO.
-template <class IO, int LBVH = -1, int EXT = 1>
-B2_HD int VolMediumStep(const RenderSceneDev &rs, PathRegs &p, float tHit, IO &io) {
+// In three parts so that the delta-tracking walk in the middle can be stepped by a persistent kernel (render.cu
+// VolMediumKernel): VolMediumBegin (sampler dimensions, the medium's spectra, the walk's start), the walk's steps
+// (TMajWalk::Step with a PathMediumCB built over the same state), VolMediumEnd (what follows the walk).
+struct VolMediumState {
+    PCG32 rng;
+    float sigA[kNLambda], sigS[kNLambda], sigT[kNLambda], T_maj[kNLambda];
+    TMajWalk walk;
+    bool terminated, scattered;
+    V3 pScatter;
+};
+
+B2_HD void VolMediumBegin(const RenderSceneDev &rs, PathRegs &p, float tHit, VolMediumState &st) {
     const MediumDev &m = rs.media[p.medium];
     ZSobol s = SamplerFor(rs, p);
     uint64_t hash0 = Hash1f(ZSobolGet1D(s));
     uint64_t hash1 = Hash1f(ZSobolGet1D(s));
-    PCG32 rng = PcgSeed(hash0, hash1);
+    st.rng = PcgSeed(hash0, hash1);
     float u = ZSobolGet1D(s);
     p.dimension = s.dimension;
-    float sigA[kNLambda], sigS[kNLambda], sigT[kNLambda], T_maj[kNLambda];
-    MediumSpectra(rs, m, p.lambdaU, sigA, sigS, sigT);
-    PathMediumCB<IO> cb(io, rng, sigA, sigS, sigT, p.depth, rs.integrator.maxDepth);
-    SampleTMaj(m, sigT, p.rayO, p.rayD, tHit, u, rng, T_maj, cb);
+    MediumSpectra(rs, m, p.lambdaU, st.sigA, st.sigS, st.sigT);
+    st.terminated = st.scattered = false;
+    st.pScatter = mk(0, 0, 0);
+    st.walk.Begin(m, p.rayO, p.rayD, tHit, u, st.T_maj);
+}
+
+// one step of the walk; TMAJ_GO_ON = call again
+template <class IO>
+B2_HD int VolMediumWalkStep(const RenderSceneDev &rs, PathRegs &p, VolMediumState &st, IO &io) {
+    PathMediumCB<IO> cb(io, st.rng, st.sigA, st.sigS, st.sigT, p.depth, rs.integrator.maxDepth);
+    int r = st.walk.Step(rs.media[p.medium], st.sigT, st.rng, st.T_maj, cb);
+    st.terminated |= cb.terminated;
+    if (cb.scattered) {
+        st.scattered = true;
+        st.pScatter = cb.pScatter;
+    }
+    return r;
+}
+
+template <class IO, int LBVH = -1, int EXT = 1>
+B2_HD int VolMediumEnd(const RenderSceneDev &rs, PathRegs &p, VolMediumState &st, IO &io);
+
+// the fast split walk of the persistent kernel (TMajFastWalk): st.walk is not used, `fw` is
+B2_HD void VolMediumBeginFast(const RenderSceneDev &rs, PathRegs &p, float tHit, VolMediumState &st, TMajFastWalk &fw) {
+    const MediumDev &m = rs.media[p.medium];
+    ZSobol s = SamplerFor(rs, p);
+    uint64_t hash0 = Hash1f(ZSobolGet1D(s));
+    uint64_t hash1 = Hash1f(ZSobolGet1D(s));
+    st.rng = PcgSeed(hash0, hash1);
+    float u = ZSobolGet1D(s);
+    p.dimension = s.dimension;
+    MediumSpectra(rs, m, p.lambdaU, st.sigA, st.sigS, st.sigT);
+    st.terminated = st.scattered = false;
+    st.pScatter = mk(0, 0, 0);
+    fw.Begin(m, p.rayO, p.rayD, tHit, u);
+}
+// the pending collision; false = the walk is over (st.T_maj all ones, as the reference leaves it)
+template <class IO>
+B2_HD bool VolMediumCollide(const RenderSceneDev &rs, PathRegs &p, VolMediumState &st, TMajFastWalk &fw, IO &io) {
+    PathMediumCB<IO> cb(io, st.rng, st.sigA, st.sigS, st.sigT, p.depth, rs.integrator.maxDepth);
+    const bool goOn = fw.Collide(rs.media[p.medium], st.sigT, st.T_maj, cb);
+    st.terminated |= cb.terminated;
+    if (cb.scattered) {
+        st.scattered = true;
+        st.pScatter = cb.pScatter;
+    }
+    if (!goOn)
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k) st.T_maj[k] = 1.f;
+    return goOn;
+}
+
+template <class IO, int LBVH = -1, int EXT = 1>
+B2_HD int VolMediumStep(const RenderSceneDev &rs, PathRegs &p, float tHit, IO &io) {
+    VolMediumState st;
+    VolMediumBegin(rs, p, tHit, st);
+    while (VolMediumWalkStep(rs, p, st, io) == TMAJ_GO_ON) {
+    }
+    return VolMediumEnd<IO, LBVH, EXT>(rs, p, st, io);
+}
+
+template <class IO, int LBVH, int EXT>
+B2_HD int VolMediumEnd(const RenderSceneDev &rs, PathRegs &p, VolMediumState &st, IO &io) {
+    const MediumDev &m = rs.media[p.medium];
+    const float *T_maj = st.T_maj;
+    struct {
+        bool terminated, scattered;
+        V3 pScatter;
+    } cb = {st.terminated, st.scattered, st.pScatter};
     if (cb.terminated || !AnyOf(io, 0) || !AnyOf(io, 1)) return VOL_TERMINATED;
     if (!cb.scattered) {
 B2_SPECTRAL_LOOP
@@ -125,7 +200,7 @@ B2_SPECTRAL_LOOP
     LightCtx ctx;
     ctx.pi = MakeP3i(pS, mk(0, 0, 0));
     ctx.n = ctx.ns = mk(0, 0, 0);
-    s = SamplerFor(rs, p);
+    ZSobol s = SamplerFor(rs, p);
     float uL = ZSobolGet1D(s);
     float uLight0, uLight1;
     ZSobolGet2D(s, uLight0, uLight1);
@@ -185,29 +260,82 @@ struct ShadowRegs {
 enum { SHADOW_BLOCKED = 0, SHADOW_REACHED = 1, SHADOW_CONTINUE = 2 };
 // T_ray / r_l / r_u: the walk's running products (all ones before the first segment).  hit: closest hit of
 // (o, d, 1 - ShadowEpsilon).  SHADOW_CONTINUE leaves the next segment's ray in sh.
-template <int EXT = 1>
-B2_HD int ShadowTrSegment(const RenderSceneDev &rs, float lambdaU, ShadowRegs &sh, const uint32_t hit[6], float *T_ray,
-                          float *r_l, float *r_u) {
-    const bool isHit = hit[0] != kMissTag;
-    uint32_t meshId = 0;
+// In three parts like VolMediumStep: ShadowTrBegin classifies the hit (SHADOW_BLOCKED at an opaque surface; otherwise
+// -1, with st.walking = the segment runs through a medium and its ratio-tracking walk has been started), the walk's
+// steps (ShadowTrWalkStep), ShadowTrEnd (the rest of the segment).
+struct ShadowTrState {
+    float sigA[kNLambda], sigS[kNLambda], sigT[kNLambda], T_maj[kNLambda];
+    TMajWalk walk;
     SurfHit si;
-    if (isHit) {
-        si = SurfHitFromRecord<EXT>(rs, sh.d, hit, &meshId);
-        if (rs.meshes[meshId].material >= 0) return SHADOW_BLOCKED;  // an opaque surface
+    uint32_t meshId;
+    bool isHit, walking;
+};
+
+template <int EXT = 1>
+B2_HD int ShadowTrBegin(const RenderSceneDev &rs, float lambdaU, ShadowRegs &sh, const uint32_t hit[6], ShadowTrState &st) {
+    st.isHit = hit[0] != kMissTag;
+    st.meshId = 0;
+    st.walking = false;
+    if (st.isHit) {
+        st.si = SurfHitFromRecord<EXT>(rs, sh.d, hit, &st.meshId);
+        if (rs.meshes[st.meshId].material >= 0) return SHADOW_BLOCKED;  // an opaque surface
     }
     if (sh.medium >= 0) {
         const MediumDev &m = rs.media[sh.medium];
         float tHit;
         memcpy(&tHit, &hit[1], 4);
-        float tMax = isHit ? tHit : (1 - kShadowEpsilon);
+        float tMax = st.isHit ? tHit : (1 - kShadowEpsilon);
         float u = PcgFloat(sh.rng);
-        float sigA[kNLambda], sigS[kNLambda], sigT[kNLambda], T_maj[kNLambda];
-        MediumSpectra(rs, m, lambdaU, sigA, sigS, sigT);
-        ShadowMediumCB cb(sh.rng, sigA, sigS, sigT, T_ray, r_l, r_u);
-        SampleTMaj(m, sigT, sh.o, sh.d, tMax, u, sh.rng, T_maj, cb);
+        MediumSpectra(rs, m, lambdaU, st.sigA, st.sigS, st.sigT);
+        st.walk.Begin(m, sh.o, sh.d, tMax, u, st.T_maj);
+        st.walking = true;
+    }
+    return -1;
+}
+
+// the fast split walk of the persistent kernel: ShadowTrBegin with `fw` started instead of st.walk
+template <int EXT = 1>
+B2_HD int ShadowTrBeginFast(const RenderSceneDev &rs, float lambdaU, ShadowRegs &sh, const uint32_t hit[6], ShadowTrState &st,
+                            TMajFastWalk &fw) {
+    st.isHit = hit[0] != kMissTag;
+    st.meshId = 0;
+    st.walking = false;
+    if (st.isHit) {
+        st.si = SurfHitFromRecord<EXT>(rs, sh.d, hit, &st.meshId);
+        if (rs.meshes[st.meshId].material >= 0) return SHADOW_BLOCKED;  // an opaque surface
+    }
+    if (sh.medium >= 0) {
+        const MediumDev &m = rs.media[sh.medium];
+        float tHit;
+        memcpy(&tHit, &hit[1], 4);
+        float tMax = st.isHit ? tHit : (1 - kShadowEpsilon);
+        float u = PcgFloat(sh.rng);
+        MediumSpectra(rs, m, lambdaU, st.sigA, st.sigS, st.sigT);
+        fw.Begin(m, sh.o, sh.d, tMax, u);
+        st.walking = true;
+    }
+    return -1;
+}
+B2_HD bool ShadowTrCollide(const RenderSceneDev &rs, ShadowRegs &sh, ShadowTrState &st, TMajFastWalk &fw, float *T_ray,
+                           float *r_l, float *r_u) {
+    ShadowMediumCB cb(sh.rng, st.sigA, st.sigS, st.sigT, T_ray, r_l, r_u);
+    const bool goOn = fw.Collide(rs.media[sh.medium], st.sigT, st.T_maj, cb);
+    if (!goOn)
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k) st.T_maj[k] = 1.f;
+    return goOn;
+}
+
+B2_HD int ShadowTrWalkStep(const RenderSceneDev &rs, ShadowRegs &sh, ShadowTrState &st, float *T_ray, float *r_l, float *r_u) {
+    ShadowMediumCB cb(sh.rng, st.sigA, st.sigS, st.sigT, T_ray, r_l, r_u);
+    return st.walk.Step(rs.media[sh.medium], st.sigT, sh.rng, st.T_maj, cb);
+}
+
+B2_HD int ShadowTrEnd(const RenderSceneDev &rs, ShadowRegs &sh, ShadowTrState &st, float *T_ray, float *r_l, float *r_u) {
+    if (st.walking) {
 B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k) {
-            float f = T_maj[k] / T_maj[0];
+            float f = st.T_maj[k] / st.T_maj[0];
             T_ray[k] *= f;
             r_l[k] *= f;
             r_u[k] *= f;
@@ -217,15 +345,27 @@ B2_SPECTRAL_LOOP
 B2_SPECTRAL_LOOP
     for (int k = 0; k < kNLambda; ++k) any |= T_ray[k] != 0;
     if (!any) return SHADOW_BLOCKED;
-    if (!isHit) return SHADOW_REACHED;
+    if (!st.isHit) return SHADOW_REACHED;
     // lightRay = si->intr.SpawnRayTo(ls->pLight) (interaction.h:110-114, ray.h:106-111)
-    V3 pf = OffsetRayOrigin(si.pi, si.n, Mid(sh.lightPi) - Mid(si.pi));
+    V3 pf = OffsetRayOrigin(st.si.pi, st.si.n, Mid(sh.lightPi) - Mid(st.si.pi));
     V3 pt = OffsetRayOrigin(sh.lightPi, sh.lightN, pf - Mid(sh.lightPi));
     sh.o = pf;
     sh.d = pt - pf;
-    sh.medium = MediumAfter(rs.meshes[meshId], si.n, sh.d, sh.medium);
+    sh.medium = MediumAfter(rs.meshes[st.meshId], st.si.n, sh.d, sh.medium);
     if (sh.d.x == 0 && sh.d.y == 0 && sh.d.z == 0) return SHADOW_REACHED;  // while (lightRay.d != Vector3f(0, 0, 0))
     return SHADOW_CONTINUE;
+}
+
+template <int EXT = 1>
+B2_HD int ShadowTrSegment(const RenderSceneDev &rs, float lambdaU, ShadowRegs &sh, const uint32_t hit[6], float *T_ray,
+                          float *r_l, float *r_u) {
+    ShadowTrState st;
+    int r = ShadowTrBegin<EXT>(rs, lambdaU, sh, hit, st);
+    if (r >= 0) return r;
+    if (st.walking)
+        while (ShadowTrWalkStep(rs, sh, st, T_ray, r_l, r_u) == TMAJ_GO_ON) {
+        }
+    return ShadowTrEnd(rs, sh, st, T_ray, r_l, r_u);
 }
 
 // The estimate a walk that reached the light returns (cpu/integrators.cpp:1397-1403, area lights): Ld(k) is

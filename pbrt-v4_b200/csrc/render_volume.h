@@ -8,13 +8,6 @@
 #include "instance.h"
 #include "render_layered.h"
 
-#ifndef B2_SPECTRAL_LOOP  // keep the 31-trip loops rolled on the device (render_path.h says why)
-#if defined(__CUDA_ARCH__)
-#define B2_SPECTRAL_LOOP _Pragma("unroll 2")
-#else
-#define B2_SPECTRAL_LOOP
-#endif
-#endif
 
 namespace b200pt {
 
@@ -199,56 +192,144 @@ B2_HD bool MajorantNext(const MediumDev &m, MajorantIter &it, MajorantSeg &seg) 
     return true;
 }
 
-// SampleT_maj (media.h:734-804).  cb(p, density, majorantScale, T_maj) is called at every tentative collision;
-// returning false ends the walk (T_maj is then all ones, as the reference returns SampledSpectrum(1)).
-// sigT[k] = sigma_a + sigma_s at the path's wavelengths (the caller fills it once per ray).
-template <class CB>
-B2_HD void SampleTMaj(const MediumDev &m, const float *sigT, V3 ro, V3 rd, float tMax, float u, PCG32 &rng, float *T_maj,
-                      CB &cb) {
-    tMax *= Length(rd);
-    rd = Normalize(rd);
-    MajorantIter it = MediumSampleRay(m, ro, rd, tMax);
+// SampleT_maj (media.h:734-804) as a resumable walk.  cb(p, density, majorantScale, T_maj) is called at every
+// tentative collision; returning false ends the walk (T_maj is then all ones, as the reference returns
+// SampledSpectrum(1)).  sigT[k] = sigma_a + sigma_s at the path's wavelengths (the caller fills it once per ray).
+// Step() is one turn of the reference's inner loop: fetch the next majorant segment when none is open, then one
+// exponential step inside it - so a warp whose lanes walk different rays (or are refilled with new ones as they
+// finish, the persistent kernels of render.cu) still executes one common body.  SampleTMaj() below runs it to the
+// end: same operations in the same order as the reference's nested loops.
+enum { TMAJ_GO_ON = 0, TMAJ_RAN_OUT = 1, TMAJ_STOPPED = 2 };
+struct TMajWalk {
+    V3 ro, rd;
+    MajorantIter it;
+    MajorantSeg seg;
+    float tMin, u;
+    bool inSeg;
+    B2_HD void Begin(const MediumDev &m, V3 o, V3 d, float tMax, float u0, float *T_maj) {
+        tMax *= Length(d);
+        ro = o;
+        rd = Normalize(d);
+        it = MediumSampleRay(m, ro, rd, tMax);
+        u = u0;
+        inSeg = false;
+        tMin = 0;
+        seg.tMin = seg.tMax = seg.scale = 0;
 B2_SPECTRAL_LOOP
-    for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
-    bool done = false;
-    while (!done) {
-        MajorantSeg seg;
-        if (!MajorantNext(m, it, seg)) return;
-        const float sigMaj0 = m.type == 0 ? sigT[0] : sigT[0] * seg.scale;
-        if (sigMaj0 == 0) {
-            float dt = seg.tMax - seg.tMin;
-            if (std::isinf(dt)) dt = 3.402823466e+38f;
-B2_SPECTRAL_LOOP
-            for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(-dt * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
-            continue;
-        }
-        float tMin = seg.tMin;
-        while (true) {
-            float t = tMin + (-logf(1 - u) / sigMaj0);  // SampleExponential (util/sampling.h:222-225)
-            u = PcgFloat(rng);
-            if (t < seg.tMax) {
-                const float nd = -(t - tMin);
-B2_SPECTRAL_LOOP
-                for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(nd * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
-                V3 p = ro + rd * t;
-                if (!cb(p, MediumDensityAt(m, p), m.type == 0 ? 1.f : seg.scale, T_maj)) {
-                    done = true;
-                    break;
-                }
-B2_SPECTRAL_LOOP
-                for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
-                tMin = t;
-            } else {
-                float dt = seg.tMax - tMin;
+        for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
+    }
+    // TMAJ_RAN_OUT: the segments are used up, T_maj holds the transmittance since the last collision;
+    // TMAJ_STOPPED: the callback ended the walk, T_maj is all ones
+    template <class CB>
+    B2_HD int Step(const MediumDev &m, const float *sigT, PCG32 &rng, float *T_maj, CB &cb) {
+        if (!inSeg) {
+            if (!MajorantNext(m, it, seg)) return TMAJ_RAN_OUT;
+            const float sigMaj0 = m.type == 0 ? sigT[0] : sigT[0] * seg.scale;
+            if (sigMaj0 == 0) {
+                float dt = seg.tMax - seg.tMin;
                 if (std::isinf(dt)) dt = 3.402823466e+38f;
 B2_SPECTRAL_LOOP
                 for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(-dt * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
-                break;
+                return TMAJ_GO_ON;
             }
+            tMin = seg.tMin;
+            inSeg = true;
         }
-    }
+        const float sigMaj0 = m.type == 0 ? sigT[0] : sigT[0] * seg.scale;
+        float t = tMin + (-logf(1 - u) / sigMaj0);  // SampleExponential (util/sampling.h:222-225)
+        u = PcgFloat(rng);
+        if (t < seg.tMax) {
+            const float nd = -(t - tMin);
 B2_SPECTRAL_LOOP
-    for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
+            for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(nd * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
+            V3 p = ro + rd * t;
+            const bool goOn = cb(p, MediumDensityAt(m, p), m.type == 0 ? 1.f : seg.scale, T_maj);
+B2_SPECTRAL_LOOP
+            for (int k = 0; k < kNLambda; ++k) T_maj[k] = 1.f;
+            if (!goOn) return TMAJ_STOPPED;
+            tMin = t;
+        } else {
+            float dt = seg.tMax - tMin;
+            if (std::isinf(dt)) dt = 3.402823466e+38f;
+B2_SPECTRAL_LOOP
+            for (int k = 0; k < kNLambda; ++k) T_maj[k] *= FastExpRef(-dt * (m.type == 0 ? sigT[k] : sigT[k] * seg.scale));
+            inSeg = false;
+        }
+        return TMAJ_GO_ON;
+    }
+};
+
+// The same walk split for the persistent kernels (render.cu): ADVANCE runs from majorant segment to majorant segment
+// with scalar work only - the reference multiplies exp(-dt sigma_maj(lambda)) into T_maj for every segment and all
+// 31 wavelengths; here the optical length  S = sum of dt * majorant scale  since the last collision is carried instead
+// and T_maj(lambda) = exp(-sigma_t(lambda) S) is formed once per collision (an exponential of the sum instead of a
+// product of exponentials: equal up to rounding, inside the image tolerance; the host check keeps Step()) - and stops
+// at a tentative collision, so that the expensive spectral part (COLLIDE: T_maj + the callback) can be run for many
+// lanes of a warp at once instead of for the two or three that happen to collide in the same step.
+enum { TMAJ_COLLISION = 3 };
+struct TMajFastWalk {
+    TMajWalk w;
+    float S, tColl;
+    B2_HD void Begin(const MediumDev &m, V3 o, V3 d, float tMax, float u0) {
+        float dummy[kNLambda];
+        w.Begin(m, o, d, tMax, u0, dummy);
+        S = 0;
+        tColl = 0;
+    }
+    B2_HD void Add(float dt, float scale) {
+        if (std::isinf(dt)) dt = 3.402823466e+38f;
+        S = fminf(S + dt * scale, 3.402823466e+38f);
+    }
+    // up to maxCells majorant segments; TMAJ_GO_ON (call again), TMAJ_RAN_OUT, or TMAJ_COLLISION at tColl
+    B2_HD int Advance(const MediumDev &m, float sigT0, PCG32 &rng, int maxCells) {
+        for (int cell = 0; cell < maxCells; ++cell) {
+            if (!w.inSeg) {
+                if (!MajorantNext(m, w.it, w.seg)) return TMAJ_RAN_OUT;
+                const float sigMaj0 = m.type == 0 ? sigT0 : sigT0 * w.seg.scale;
+                if (sigMaj0 == 0) {
+                    Add(w.seg.tMax - w.seg.tMin, m.type == 0 ? 1.f : w.seg.scale);
+                    continue;
+                }
+                w.tMin = w.seg.tMin;
+                w.inSeg = true;
+            }
+            const float scale = m.type == 0 ? 1.f : w.seg.scale;
+            float t = w.tMin + (-logf(1 - w.u) / (sigT0 * scale));
+            w.u = PcgFloat(rng);
+            if (t < w.seg.tMax) {
+                Add(t - w.tMin, scale);
+                tColl = t;
+                return TMAJ_COLLISION;
+            }
+            Add(w.seg.tMax - w.tMin, scale);
+            w.inSeg = false;
+        }
+        return TMAJ_GO_ON;
+    }
+    // transmittance since the last collision
+    B2_HD void TMaj(const float *sigT, float *T_maj) const {
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k) T_maj[k] = sigT[k] == 0 ? 1.f : FastExpRef(-(sigT[k] * S));
+    }
+    // the pending collision: false = the callback ended the walk
+    template <class CB>
+    B2_HD bool Collide(const MediumDev &m, const float *sigT, float *T_maj, CB &cb) {
+        TMaj(sigT, T_maj);
+        V3 p = w.ro + w.rd * tColl;
+        const bool goOn = cb(p, MediumDensityAt(m, p), m.type == 0 ? 1.f : w.seg.scale, T_maj);
+        S = 0;
+        w.tMin = tColl;
+        return goOn;
+    }
+};
+
+template <class CB>
+B2_HD void SampleTMaj(const MediumDev &m, const float *sigT, V3 ro, V3 rd, float tMax, float u, PCG32 &rng, float *T_maj,
+                      CB &cb) {
+    TMajWalk w;
+    w.Begin(m, ro, rd, tMax, u, T_maj);
+    while (w.Step(m, sigT, rng, T_maj, cb) == TMAJ_GO_ON) {
+    }
 }
 
 // SampleDiscrete over {pAbsorb, pScatter, pNull} (util/sampling.h:79-113)
