@@ -271,7 +271,9 @@ typedef struct b200pt_render_desc {
     float camera_from_raster[16];
     float render_from_camera[16];
     float lens_radius, focal_distance;
-    /* film: 0 = RGBFilm (film.h:232-310), 1 = SpectralFilm (film.h:430-560; n_buckets below), box filter */
+    /* film: 0 = RGBFilm (film.h:232-310), 1 = SpectralFilm (film.h:430-560; n_buckets below), 2 = GBufferFilm, the
+     * ISET spectral film (film.h:322-408, film.cpp:597-666: 31 radiance buckets over 395..705 nm + AOVs; fields at
+     * the end of this struct); box filter */
     uint32_t film_type;
     int32_t pixel_bounds[4]; /* x0 y0 x1 y1 */
     int32_t full_resolution[2];
@@ -350,6 +352,15 @@ typedef struct b200pt_render_desc {
     const float *microlens_offsets;
     float microlens_offset_from_sensor;
     int32_t microlens_simulation_radius;
+    /* film_type 2 = GBufferFilm.  Radiance buckets: n_buckets = 31 over [395, 705] nm is hard-coded in the reference
+     * (film.h:383-389) and required here.  gbuffer_output_from_render / _inv: the transform (m, mInv, row major) that
+     * takes the first visible surface from render space to the AOVs' output space - for the default "camera"
+     * coordinate system that is the INVERSE of GBufferFilm::outputFromRender (applyInverse, film.cpp:1088-1090), i.e.
+     * CameraFromRender.  material_ids[n_materials]: Material::materialId of each material (materials.cpp:738), NULL =
+     * 1 + index.  Not built: Albedo.*, dzdx / dzdy (they need bsdf.rho and camera-ray differentials) and the SVD basis. */
+    float gbuffer_output_from_render[16];
+    float gbuffer_output_from_render_inv[16];
+    const int32_t *material_ids;
 } b200pt_render_desc;
 
 typedef struct b200pt_render b200pt_render;
@@ -380,6 +391,17 @@ int b200pt_film_read(b200pt_render *r, double *rgb_weight);
 int b200pt_film_spectral_image(b200pt_render *r, float *buckets);
 /* final image, 3 floats per pixel: outputRGBFromSensorRGB * (rgbSum / weightSum) (film.h:261-277) */
 int b200pt_film_image(b200pt_render *r, float *rgb);
+/* GBufferFilm::GetImage (film.cpp:743-1044) for film_type 2: R, G, B and, in the reference's channel order, the groups
+ * selected in `channels` (the film's save* switches, film.cpp:1062-1073): Radiance.C01-31 (bucket sum / sum of all sample
+ * weights: the CPU build's observed behaviour), P.X-Z, MaterialId, InstanceId, Ns.X-Z, N.X-Z,
+ * Variance.R-B, RelativeVariance.R-B.  out: height x width x (*n_channels) floats, channels last; out == NULL only
+ * reports *n_channels.  Under multi-GPU rendering the sums reduce with the film buffer; the two id channels are this
+ * rank's (the reference keeps the last sample's). */
+enum {
+    B200PT_GBUFFER_RADIANCE = 1, B200PT_GBUFFER_POSITION = 2, B200PT_GBUFFER_MATERIAL = 4, B200PT_GBUFFER_INSTANCE = 8,
+    B200PT_GBUFFER_NS = 16, B200PT_GBUFFER_NORMAL = 32, B200PT_GBUFFER_VARIANCE = 64, B200PT_GBUFFER_RELATIVE_VARIANCE = 128
+};
+int b200pt_film_gbuffer_image(b200pt_render *r, uint32_t channels, float *out, int32_t *n_channels);
 int b200pt_render_get_stats(const b200pt_render *r, b200pt_render_stats *out);
 
 /* Host-only: build the binary SAH BVH for one primitive list exactly as the

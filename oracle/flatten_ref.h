@@ -249,8 +249,23 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         w.u32("film_type", {1}, {1});
         dumpFilm(sf);
         w.f32("film_spectral", {3}, {float(sf->nBuckets), sf->lambdaMin, sf->lambdaMax});
+    } else if (film.Is<GBufferFilm>()) {  // film.h:322-408, the ISET spectral film
+        const GBufferFilm *gf = film.Cast<GBufferFilm>();
+        w.u32("film_type", {1}, {2});
+        dumpFilm(gf);
+        w.f32("film_spectral", {3}, {31.f, 395.f, 705.f});  // LambdaToBucket, film.h:383-389
+        // the AOVs' space: ApplyInverse(outputFromRender) for "camera" (film.cpp:1088-1090), outputFromRender for "world"
+        Transform ofr = gf->outputFromRender.startTransform;
+        Transform eff = gf->applyInverse ? Inverse(ofr) : ofr;
+        std::vector<float> m(16), mi(16);
+        for (int i = 0; i < 16; ++i) {
+            m[i] = eff.GetMatrix()[i / 4][i % 4];
+            mi[i] = eff.GetInverseMatrix()[i / 4][i % 4];
+        }
+        w.f32("gbuffer_from_render", {16}, m);
+        w.f32("gbuffer_from_render_inv", {16}, mi);
     } else
-        die("only the rgb and spectral films are dumped so far");
+        die("only the rgb, spectral and gbuffer films are dumped so far");
 
     // ---- sampler
     if (sampler.Is<ZSobolSampler>()) {
@@ -629,6 +644,11 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             die("only diffuse, conductor, dielectric and coateddiffuse materials are dumped so far");
         matI.insert(matI.end(), rec, rec + 5);
         matF.insert(matF.end(), prm, prm + 8);
+    }
+    {  // Material::materialId (materials.cpp:738), GBufferFilm's MaterialId channel
+        std::vector<int32_t> ids;
+        for (pbrt::Material mtl : materialList) ids.push_back(mtl ? int32_t(mtl.materialId) : 0);
+        w.i32("material_ids", {uint32_t(ids.size())}, ids);
     }
     w.i32("materials_i", {uint32_t(materialList.size()), 5}, matI);
     w.f32("materials_f", {uint32_t(materialList.size()), 8}, matF);

@@ -182,7 +182,13 @@ class RenderDesc(C.Structure):
                 ("n_microlens_elements", C.c_uint32), ("microlens_elements", C.POINTER(C.c_float)),
                 ("microlens_element_transforms", C.POINTER(C.c_float)), ("microlens_dims", C.c_int32 * 2),
                 ("microlens_offsets", C.POINTER(C.c_float)), ("microlens_offset_from_sensor", C.c_float),
-                ("microlens_simulation_radius", C.c_int32)]
+                ("microlens_simulation_radius", C.c_int32),
+                ("gbuffer_output_from_render", C.c_float * 16), ("gbuffer_output_from_render_inv", C.c_float * 16),
+                ("material_ids", C.POINTER(C.c_int32))]
+
+
+GBUFFER_RADIANCE, GBUFFER_POSITION, GBUFFER_MATERIAL, GBUFFER_INSTANCE = 1, 2, 4, 8
+GBUFFER_NS, GBUFFER_NORMAL, GBUFFER_VARIANCE, GBUFFER_RELATIVE_VARIANCE = 16, 32, 64, 128
 
 
 class RenderStats(C.Structure):
@@ -198,6 +204,7 @@ SYMBOLS.update({
     "b200pt_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "b200pt_film_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "b200pt_film_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "b200pt_film_gbuffer_image": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "b200pt_film_spectral_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "b200pt_render_get_stats": (C.c_int, [C.c_void_p, C.POINTER(RenderStats)]),
 })

@@ -13,6 +13,7 @@
 
 #include <algorithm>
 
+#include "../../include/b200pt.h"
 #include "render_core.h"
 #include "render_kernels.h"
 
@@ -30,8 +31,9 @@ static size_t Al(size_t b) { return (b + 255) & ~size_t(255); }
 #endif
 
 #if B2_RENDER_PART == 0
-size_t PassBufferBytes(long long n, int depthSlots, bool vol) {
+size_t PassBufferBytes(long long n, int depthSlots, bool vol, bool aov) {
     size_t t = 0;
+    if (aov) t += Al(sizeof(float) * kAovWords * n);
     if (vol)
         t += 5 * Al(sizeof(float) * kNLambda * n) + Al(sizeof(uint32_t) * kShadowAuxWords * n) +
              Al(sizeof(uint32_t) * 6 * n) + Al(2 * sizeof(int));
@@ -47,7 +49,7 @@ size_t PassBufferBytes(long long n, int depthSlots, bool vol) {
     return t;
 }
 
-void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuffers &pb) {
+void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuffers &pb, bool aov) {
     char *p = static_cast<char *>(base);
     auto take = [&](size_t b) {
         char *r = p;
@@ -73,6 +75,7 @@ void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuf
     pb.ru = pb.rl = pb.shT = pb.shRl = pb.shRu = nullptr;
     pb.shAux = pb.shHits = nullptr;
     pb.shContinue = nullptr;
+    pb.aov = aov ? (float *)take(sizeof(float) * kAovWords * n) : nullptr;
     if (vol) {
         pb.ru = (float *)take(sizeof(float) * kNLambda * n);
         pb.rl = (float *)take(sizeof(float) * kNLambda * n);
@@ -154,6 +157,17 @@ struct DevIO {
     __device__ __forceinline__ float Beta(int k) const { return beta[k * kShadeBlock]; }
     __device__ __forceinline__ void SetBeta(int k, float v) { beta[k * kShadeBlock] = v; }
     __device__ __forceinline__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
+    __device__ __forceinline__ void VisibleSurface(V3 p, V3 n, V3 ns, int material, int instance) {
+        if (!pb.aov) return;
+        float *a = pb.aov + path;
+        const long long N = pb.n;
+        a[0] = 1.f;
+        a[1 * N] = p.x; a[2 * N] = p.y; a[3 * N] = p.z;
+        a[4 * N] = n.x; a[5 * N] = n.y; a[6 * N] = n.z;
+        a[7 * N] = ns.x; a[8 * N] = ns.y; a[9 * N] = ns.z;
+        a[10 * N] = (float)material;
+        a[11 * N] = (float)instance;
+    }
     __device__ __forceinline__ void ShadowBegin() { slot = QueuePush(nShadow); }
     __device__ __forceinline__ void SetLd(int k, float v) { pb.Ld[(long long)k * pb.n + slot] = v; }
     __device__ __forceinline__ void ShadowEnd(bool valid, V3 o, V3 d, float tMax) {
@@ -186,6 +200,7 @@ struct GlobalIO {
     int *nShadow;
     int slot;
     __device__ GlobalIO(const PassBuffers &b, int pathId, int *shadowCount) : pb(b), path(pathId), nShadow(shadowCount), slot(-1) {}
+    __device__ __forceinline__ void VisibleSurface(V3, V3, V3, int, int) {}
     __device__ __forceinline__ float Beta(int k) const { return pb.beta[(long long)k * pb.n + path]; }
     __device__ __forceinline__ void SetBeta(int k, float v) { pb.beta[(long long)k * pb.n + path] = v; }
     __device__ __forceinline__ float Ru(int k) const { return pb.ru[(long long)k * pb.n + path]; }
@@ -252,6 +267,7 @@ GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nA
             pb.rl[k * n + i] = 1.f;
         }
     }
+    if (pb.aov) pb.aov[i] = 0.f;  // no VisibleSurface yet
     StoreHeader(pb, i, p);
     pb.scalars[kCameraWeightScalar * n + i] = p.cameraWeight;
     // a sample without a camera ray (vignetted by the lens system) keeps its queue slot with a ray that
@@ -671,6 +687,112 @@ __global__ void FilmAddSpectralKernel(FilmDev fd, PassBuffers pb, int nPixels, i
     }
 }
 
+// GBufferFilm::AddSample (film.cpp:597-666) beyond the RGB sums and the 31 radiance buckets (which are the spectral
+// film's: FilmAddSpectralKernel): the VisibleSurface AOVs.  One thread per pixel, samples in index order; the sums are
+// kept in double (the reference's are float, its variance a float Welford update: equal within the image tolerance);
+// materialId / instanceId are the last sample's, as in the reference, and live outside the summed film (`ids`).
+__global__ void FilmAddGBufferKernel(FilmDev fd, PassBuffers pb, int nPixels, int nSamplesInPass, double *film, float *ids,
+                                     const int32_t *materialIds) {
+    int pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= nPixels) return;
+    double *g = film + (4ll + 2ll * fd.nBuckets) * nPixels + pix;  // plane q at g[q * nPixels]
+    const long long n = pb.n, P = nPixels;
+    const float *M = fd.outM, *I = fd.outMInv;
+    double acc[kGBufferPlanes];
+    for (int q = 0; q < kGBufferPlanes; ++q) acc[q] = g[q * P];
+    float idM = ids[pix], idI = ids[P + pix];
+    for (int s = 0; s < nSamplesInPass; ++s) {
+        const long long path = (long long)s * nPixels + pix;
+        const float4 v = reinterpret_cast<const float4 *>(pb.rgbw)[path];
+        const float *a = pb.aov + path;
+        if (a[0] != 0.f && v.w != 0.f) {
+            const float w = v.w;
+            const float px = a[1 * n], py = a[2 * n], pz = a[3 * n];
+            // Transform::operator()(Point3f) (util/transform.h:270-281) and (Normal3f) = transpose(mInv) n (:300-306)
+            float xp = M[0] * px + M[1] * py + M[2] * pz + M[3], yp = M[4] * px + M[5] * py + M[6] * pz + M[7];
+            float zp = M[8] * px + M[9] * py + M[10] * pz + M[11], wp = M[12] * px + M[13] * py + M[14] * pz + M[15];
+            if (wp != 1) { xp /= wp; yp /= wp; zp /= wp; }
+            acc[0] += w;
+            acc[1] += w * xp; acc[2] += w * yp; acc[3] += w * zp;
+            for (int k = 0; k < 2; ++k) {
+                const float nx = a[(4 + 3 * k) * n], ny = a[(5 + 3 * k) * n], nz = a[(6 + 3 * k) * n];
+                acc[4 + 3 * k] += w * (I[0] * nx + I[4] * ny + I[8] * nz);
+                acc[5 + 3 * k] += w * (I[1] * nx + I[5] * ny + I[9] * nz);
+                acc[6 + 3 * k] += w * (I[2] * nx + I[6] * ny + I[10] * nz);
+            }
+            const float rgb[3] = {v.x / w, v.y / w, v.z / w};
+            for (int c = 0; c < 3; ++c) {
+                acc[10 + c] += rgb[c];
+                acc[13 + c] += double(rgb[c]) * rgb[c];
+            }
+            acc[16] += 1;
+        }
+        // p.materialId = visibleSurface->materialId: every sample writes it; a sample without a VisibleSurface leaves
+        // what a default-constructed one holds (indeterminate in the reference; 0 here)
+        const int mi = a[0] != 0.f ? (int)a[10 * n] : -1;
+        idM = mi < 0 ? 0.f : (materialIds ? (float)materialIds[mi] : (float)(mi + 1));
+        idI = a[0] != 0.f ? a[11 * n] : 0.f;
+    }
+    for (int q = 0; q < kGBufferPlanes; ++q) g[q * P] = acc[q];
+    ids[pix] = idM;
+    ids[P + pix] = idI;
+}
+
+// GBufferFilm::GetImage (film.cpp:743-1044), channels-last float image.  Radiance.Cxx = L[b] / rgbWeightSum - the
+// bucket sum over the sum of ALL sample weights, not the bucket's own: `pixel.LSplat` is never allocated, so the
+// per-bucket normalisation of film.cpp:889-894 does not run.
+__global__ void FilmGBufferImageKernel(FilmDev film, const double *acc, const float *ids, int nPixels, uint32_t channels,
+                                       int nChannels, float *out) {
+    int pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= nPixels) return;
+    const long long P = nPixels;
+    const double *a = acc + 4ll * pix;
+    float *o = out + (long long)nChannels * pix;
+    float r = (float)a[0], g = (float)a[1], b = (float)a[2], w = (float)a[3];
+    if (w != 0) { r /= w; g /= w; b /= w; }
+    const float *m = film.outputRGBFromSensorRGB;
+    int c = 0;
+    o[c++] = m[0] * r + m[1] * g + m[2] * b;
+    o[c++] = m[3] * r + m[4] * g + m[5] * b;
+    o[c++] = m[6] * r + m[7] * g + m[8] * b;
+    if (channels & B200PT_GBUFFER_RADIANCE)
+        for (int k = 0; k < film.nBuckets; ++k) {
+            float L = (float)acc[(4ll + k) * P + pix];
+            o[c++] = w != 0 ? L / w : L;
+        }
+    const double *gq = acc + (4ll + 2ll * film.nBuckets) * P + pix;
+    const float gw = (float)gq[0];
+    if (channels & B200PT_GBUFFER_POSITION)
+        for (int k = 0; k < 3; ++k) {
+            float v = (float)gq[(1 + k) * P];
+            o[c++] = gw != 0 ? v / gw : v;
+        }
+    if (channels & B200PT_GBUFFER_MATERIAL) o[c++] = ids[pix];
+    if (channels & B200PT_GBUFFER_INSTANCE) o[c++] = ids[P + pix];
+    for (int which = 1; which >= 0; --which) {  // Ns before N (film.cpp:812-825)
+        if (!(channels & (which ? B200PT_GBUFFER_NS : B200PT_GBUFFER_NORMAL))) continue;
+        float nx = (float)gq[(4 + 3 * which) * P], ny = (float)gq[(5 + 3 * which) * P], nz = (float)gq[(6 + 3 * which) * P];
+        float l2 = nx * nx + ny * ny + nz * nz;
+        if (l2 > 0) {
+            float l = sqrtf(l2);
+            nx /= l; ny /= l; nz /= l;
+        } else
+            nx = ny = nz = 0;
+        o[c++] = nx; o[c++] = ny; o[c++] = nz;
+    }
+    const double cnt = gq[16 * P];
+    float var[3], mean[3];
+    for (int k = 0; k < 3; ++k) {  // VarianceEstimator (util/math.h): S / (n - 1), relative = variance / mean
+        const double s1 = gq[(10 + k) * P], s2 = gq[(13 + k) * P];
+        mean[k] = cnt > 0 ? (float)(s1 / cnt) : 0.f;
+        var[k] = cnt > 1 ? (float)(fmax(s2 - s1 * s1 / cnt, 0.0) / (cnt - 1)) : 0.f;
+    }
+    if (channels & B200PT_GBUFFER_VARIANCE)
+        for (int k = 0; k < 3; ++k) o[c++] = var[k];
+    if (channels & B200PT_GBUFFER_RELATIVE_VARIANCE)
+        for (int k = 0; k < 3; ++k) o[c++] = (cnt < 1 || mean[k] == 0) ? 0.f : var[k] / mean[k];
+}
+
 // SpectralFilm::GetImage's spectral channels (film.cpp:1262-1272): bucketSums / weightSums in double, to float
 __global__ void FilmSpectralImageKernel(int nBuckets, const double *acc, int nPixels, float *out) {
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -840,6 +962,16 @@ cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass
 cudaError_t LaunchFilmAddSpectral(const FilmDev &film, const PassBuffers &pb, int nPixels, int nSamplesInPass,
                                   double *acc, cudaStream_t stream) {
     FilmAddSpectralKernel<<<Blocks(nPixels, 128), 128, 0, stream>>>(film, pb, nPixels, nSamplesInPass, acc);
+    return cudaGetLastError();
+}
+cudaError_t LaunchFilmAddGBuffer(const FilmDev &film, const PassBuffers &pb, int nPixels, int nSamplesInPass, double *acc,
+                                 float *ids, const int32_t *materialIds, cudaStream_t stream) {
+    FilmAddGBufferKernel<<<Blocks(nPixels, 128), 128, 0, stream>>>(film, pb, nPixels, nSamplesInPass, acc, ids, materialIds);
+    return cudaGetLastError();
+}
+cudaError_t LaunchFilmGBufferImage(const FilmDev &film, const double *acc, const float *ids, int nPixels, uint32_t channels,
+                                   int nChannels, float *out, cudaStream_t stream) {
+    FilmGBufferImageKernel<<<Blocks(nPixels, 128), 128, 0, stream>>>(film, acc, ids, nPixels, channels, nChannels, out);
     return cudaGetLastError();
 }
 cudaError_t LaunchFilmSpectralImage(const FilmDev &film, const double *acc, int nPixels, float *out,

@@ -23,7 +23,8 @@ struct b200pt_render {
     RenderSceneDev dev{};
     void *dSpectra = nullptr, *dMaterials = nullptr, *dLights = nullptr, *dMeshes = nullptr;
     void *dLightBvh = nullptr, *dBitTrails = nullptr, *dInfinite = nullptr;
-    void *dLens = nullptr, *dPupil = nullptr, *dCornerAttr = nullptr;
+    void *dLens = nullptr, *dPupil = nullptr, *dCornerAttr = nullptr, *dMaterialIds = nullptr;
+    float *dFilmIds = nullptr;  // GBufferFilm: materialId / instanceId of the last sample per pixel (2 x nPixels)
     void *dMedia = nullptr;
     std::vector<void *> dGrids;  // density and majorant grids of the media
     double *dFilm = nullptr;
@@ -64,6 +65,8 @@ int b200pt_render_destroy(b200pt_render *r) {
     }
     cudaFree(r->dSpectra);
     cudaFree(r->dMaterials);
+    cudaFree(r->dMaterialIds);
+    cudaFree(r->dFilmIds);
     cudaFree(r->dLights);
     cudaFree(r->dMeshes);
     cudaFree(r->dLightBvh);
@@ -109,7 +112,8 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         (rc = Upload(ctx, r->host.lightBvhNodes, &r->dLightBvh)) ||
         (rc = Upload(ctx, r->host.lightBitTrails, &r->dBitTrails)) ||
         (rc = Upload(ctx, r->host.infiniteLights, &r->dInfinite)) || (rc = Upload(ctx, r->host.lens, &r->dLens)) ||
-        (rc = Upload(ctx, r->host.pupilBounds, &r->dPupil)) || (rc = Upload(ctx, r->host.cornerAttr, &r->dCornerAttr)))
+        (rc = Upload(ctx, r->host.pupilBounds, &r->dPupil)) || (rc = Upload(ctx, r->host.cornerAttr, &r->dCornerAttr)) ||
+        (rc = Upload(ctx, r->host.materialIds, &r->dMaterialIds)))
         return fail(rc);
     for (size_t i = 0; i < r->host.media.size(); ++i) {  // grids first: the medium table points at them
         if (r->host.media[i].type != 1) continue;
@@ -127,6 +131,7 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     r->dev.media = (const MediumDev *)r->dMedia;
     r->dev.spectra = (const SpectrumTable *)r->dSpectra;
     r->dev.materials = (const MaterialDev *)r->dMaterials;
+    r->dev.materialIds = r->host.materialIds.empty() ? nullptr : (const int32_t *)r->dMaterialIds;
     r->dev.lights = (const LightDev *)r->dLights;
     r->dev.meshes = (const MeshAttrDev *)r->dMeshes;
     r->dev.lightBvhNodes = r->dLightBvh;
@@ -145,7 +150,7 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         size_t freeB = 0, totalB = 0;
         if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
             const bool volPath = r->dev.integrator.type == 1;
-            const size_t perPath = PassBufferBytes(1 << 20, volPath ? kVolMaxIterations + 2 : r->dev.integrator.maxDepth + 2, volPath) >> 20;
+            const size_t perPath = PassBufferBytes(1 << 20, volPath ? kVolMaxIterations + 2 : r->dev.integrator.maxDepth + 2, volPath, r->dev.film.type == 2) >> 20;
             const long long fit = (long long)(0.4 * double(freeB) / double(std::max<size_t>(perPath, 1)));
             r->maxPathsPerPass = std::max(4ll << 20, std::min(32ll << 20, fit));
         } else {
@@ -153,9 +158,15 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         }
     }
     if (const char *v = getenv("B200PT_PASS_PATHS")) r->maxPathsPerPass = std::max(1ll, atoll(v));
-    r->filmDoubles = size_t(r->nPixels) * (4 + 2 * size_t(r->dev.film.nBuckets));
+    r->filmDoubles = size_t(r->nPixels) * (4 + 2 * size_t(r->dev.film.nBuckets) + (r->dev.film.type == 2 ? kGBufferPlanes : 0));
+    if (r->dev.film.type == 2 &&
+        (cudaMalloc((void **)&r->dFilmIds, sizeof(float) * 2 * size_t(r->nPixels)) != cudaSuccess ||
+         cudaMemsetAsync(r->dFilmIds, 0, sizeof(float) * 2 * size_t(r->nPixels), ctx->stream) != cudaSuccess)) {
+        ctx->err = "render setup: gbuffer id planes";
+        return fail(B200PT_ERR_CUDA);
+    }
     if (cudaMalloc((void **)&r->dFilm, sizeof(double) * r->filmDoubles) != cudaSuccess ||
-        cudaMalloc((void **)&r->dImage, sizeof(float) * std::max(3, r->dev.film.nBuckets) * size_t(r->nPixels)) != cudaSuccess ||
+        cudaMalloc((void **)&r->dImage, sizeof(float) * std::max(3, r->dev.film.nBuckets + 32) * size_t(r->nPixels)) != cudaSuccess ||
         cudaMalloc((void **)&r->dCounters, 4 * sizeof(unsigned long long)) != cudaSuccess ||
         cudaEventCreate(&r->ev0) != cudaSuccess || cudaEventCreate(&r->ev1) != cudaSuccess ||
         cudaMemsetAsync(r->dFilm, 0, sizeof(double) * r->filmDoubles, ctx->stream) != cudaSuccess ||
@@ -173,6 +184,7 @@ int b200pt_film_clear(b200pt_render *r) {
     b200pt_ctx *ctx = r->scene->ctx;
     B2_CUDA(ctx, cudaSetDevice(ctx->device));
     B2_CUDA(ctx, cudaMemsetAsync(r->dFilm, 0, sizeof(double) * r->filmDoubles, ctx->stream));
+    if (r->dFilmIds) B2_CUDA(ctx, cudaMemsetAsync(r->dFilmIds, 0, sizeof(float) * 2 * size_t(r->nPixels), ctx->stream));
     return B200PT_OK;
 }
 
@@ -202,12 +214,12 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
         cudaFree(r->dPaths);
         r->dPaths = nullptr;
         r->pathCap = 0;
-        if (cudaMalloc(&r->dPaths, PassBufferBytes(need, depthSlots, vol)) != cudaSuccess) {
+        if (cudaMalloc(&r->dPaths, PassBufferBytes(need, depthSlots, vol, r->dev.film.type == 2)) != cudaSuccess) {
             (void)cudaGetLastError();
             ctx->err = "render_run: out of device memory for the path buffers";
             return B200PT_ERR_NOMEM;
         }
-        CarvePassBuffers(r->dPaths, need, depthSlots, vol, r->pb);
+        CarvePassBuffers(r->dPaths, need, depthSlots, vol, r->pb, r->dev.film.type == 2);
         r->pathCap = need;
     }
     const PassBuffers &pb = r->pb;
@@ -262,8 +274,12 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
             }
             B2_CUDA(ctx, LaunchFinish(r->dev, pb, nActive, ctx->stream));
             B2_CUDA(ctx, LaunchFilmAdd(pb, nPix, ns, r->dFilm, ctx->stream));
-            if (r->dev.film.type == 1) {
+            if (r->dev.film.type >= 1) {
                 B2_CUDA(ctx, LaunchFilmAddSpectral(r->dev.film, pb, nPix, ns, r->dFilm, ctx->stream));
+                ++launches;
+            }
+            if (r->dev.film.type == 2) {
+                B2_CUDA(ctx, LaunchFilmAddGBuffer(r->dev.film, pb, nPix, ns, r->dFilm, r->dFilmIds, r->dev.materialIds, ctx->stream));
                 ++launches;
             }
             B2_CUDA(ctx, LaunchSumCounts(pb, usedIters, r->dCounters, ctx->stream));
@@ -291,8 +307,12 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
         }
         B2_CUDA(ctx, LaunchFinish(r->dev, pb, nActive, ctx->stream));
         B2_CUDA(ctx, LaunchFilmAdd(pb, nPix, ns, r->dFilm, ctx->stream));
-        if (r->dev.film.type == 1) {
+        if (r->dev.film.type >= 1) {
             B2_CUDA(ctx, LaunchFilmAddSpectral(r->dev.film, pb, nPix, ns, r->dFilm, ctx->stream));
+            ++launches;
+        }
+        if (r->dev.film.type == 2) {
+            B2_CUDA(ctx, LaunchFilmAddGBuffer(r->dev.film, pb, nPix, ns, r->dFilm, r->dFilmIds, r->dev.materialIds, ctx->stream));
             ++launches;
         }
         B2_CUDA(ctx, LaunchSumCounts(pb, maxDepth + 1, r->dCounters, ctx->stream));
@@ -332,10 +352,35 @@ int b200pt_film_image(b200pt_render *r, float *rgb) {
     return B200PT_OK;
 }
 
+int b200pt_film_gbuffer_image(b200pt_render *r, uint32_t channels, float *out, int32_t *n_channels) {
+    if (!r || !n_channels) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    if (r->dev.film.type != 2) {
+        ctx->err = "b200pt_film_gbuffer_image: the film is not a gbuffer film";
+        return B200PT_ERR_INVALID;
+    }
+    int nc = 3;
+    if (channels & B200PT_GBUFFER_RADIANCE) nc += r->dev.film.nBuckets;
+    if (channels & B200PT_GBUFFER_POSITION) nc += 3;
+    if (channels & B200PT_GBUFFER_MATERIAL) nc += 1;
+    if (channels & B200PT_GBUFFER_INSTANCE) nc += 1;
+    if (channels & B200PT_GBUFFER_NS) nc += 3;
+    if (channels & B200PT_GBUFFER_NORMAL) nc += 3;
+    if (channels & B200PT_GBUFFER_VARIANCE) nc += 3;
+    if (channels & B200PT_GBUFFER_RELATIVE_VARIANCE) nc += 3;
+    *n_channels = nc;
+    if (!out) return B200PT_OK;
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    B2_CUDA(ctx, LaunchFilmGBufferImage(r->dev.film, r->dFilm, r->dFilmIds, r->nPixels, channels, nc, r->dImage, ctx->stream));
+    B2_CUDA(ctx, cudaMemcpyAsync(out, r->dImage, sizeof(float) * size_t(nc) * r->nPixels, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200PT_OK;
+}
+
 int b200pt_film_spectral_image(b200pt_render *r, float *buckets) {
     if (!r || !buckets) return B200PT_ERR_INVALID;
     b200pt_ctx *ctx = r->scene->ctx;
-    if (r->dev.film.type != 1) {
+    if (r->dev.film.type != 1) {  // (a gbuffer film's buckets come out through b200pt_film_gbuffer_image)
         ctx->err = "b200pt_film_spectral_image: the film is not a spectral film";
         return B200PT_ERR_INVALID;
     }

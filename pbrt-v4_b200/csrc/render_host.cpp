@@ -43,7 +43,9 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("omni camera: microlens simulation radius must be 0..8");
         }
     }
-    if (d->film_type > 1) return bad("unsupported film type");
+    if (d->film_type > 2) return bad("unsupported film type");
+    if (d->film_type == 2 && (d->n_buckets != 31 || d->lambda_min != 395.f || d->lambda_max != 705.f))
+        return bad("gbuffer film: 31 buckets over 395..705 nm (hard-coded in the reference, film.h:383-389)");
     if (d->film_type == 1) {
         if (d->n_buckets < 1 || d->n_buckets > 64) return bad("spectral film: n_buckets must be 1..64");
         if (d->lambda_min != 395.f || d->lambda_max != 705.f)
@@ -108,7 +110,13 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     rs.camera.lensRadius = d->lens_radius;
     rs.camera.focalDistance = d->focal_distance;
     rs.film.type = d->film_type;
-    rs.film.nBuckets = d->film_type == 1 ? int32_t(d->n_buckets) : 0;
+    rs.film.nBuckets = d->film_type >= 1 ? int32_t(d->n_buckets) : 0;
+    if (d->film_type == 2) {
+        std::memcpy(rs.film.outM, d->gbuffer_output_from_render, 64);
+        std::memcpy(rs.film.outMInv, d->gbuffer_output_from_render_inv, 64);
+        out.materialIds.resize(d->n_materials);
+        for (uint32_t i = 0; i < d->n_materials; ++i) out.materialIds[i] = d->material_ids ? d->material_ids[i] : int32_t(i + 1);
+    }
     rs.film.x0 = d->pixel_bounds[0];
     rs.film.y0 = d->pixel_bounds[1];
     rs.film.x1 = d->pixel_bounds[2];

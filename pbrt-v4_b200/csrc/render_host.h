@@ -24,6 +24,7 @@ struct RenderHost {
     std::vector<std::pair<std::vector<float>, std::vector<float>>> mediumGrids;  // per medium: density, majorants
     std::vector<float> cornerAttr;         // per-corner normals / uv (MeshAttrDev::nOff, uvOff)
     std::vector<float> lens, pupilBounds;  // realistic camera: 4 floats per element / per film-radius bin
+    std::vector<int32_t> materialIds;      // GBufferFilm: the host's Material::materialId per material
     int width = 0, height = 0;
 };
 

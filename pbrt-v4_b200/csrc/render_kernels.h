@@ -16,6 +16,10 @@ constexpr uint32_t kConsumedTag = 0xFFFFFFFDu;  // hit slot of a ray the medium 
 constexpr int kVolMaxIterations = 96;  // wavefront iterations of a volpath pass (interfaces do not count as depth)
 constexpr int kMatQueues = 4;     // one shading queue per MaterialType
 constexpr int kCountStride = 8;   // ints per depth in PassBuffers::counts
+constexpr int kAovWords = 12;     // PassBuffers::aov planes
+// GBufferFilm accumulators behind the rgbw and the 2 x 31 bucket planes, one plane of nPixels doubles each:
+// gBufferWeightSum, pSum[3], nSum[3], nsSum[3], sum rgb[3], sum rgb^2[3], n (VarianceEstimator as sums)
+constexpr int kGBufferPlanes = 17;
 
 // One pass = nPixels x nSamplesInPass paths; path i is pixel i % nPixels, sample slot i / nPixels.
 // Path state is indexed by path id and laid out [field][path] so a warp's accesses coalesce; the
@@ -31,6 +35,7 @@ struct PassBuffers {
     float *scalars;        // kPathScalars x n
     int *ints;             // kPathInts x n
     float *rgbw;           // n x 4    finished sample: weight * sensor rgb, weight
+    float *aov;            // kAovWords x n, GBufferFilm only (else null): the sample's VisibleSurface {set, p, n, ns, material, instance}
     // ---- per queue slot
     float *rays[2];        // n x 7 {o, d, tMax}, current / next depth
     int *rayPath[2];       // n     path id of the ray in that slot
@@ -52,8 +57,8 @@ struct PassBuffers {
     int maxDepthSlots;
 };
 
-size_t PassBufferBytes(long long n, int depthSlots, bool vol);
-void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuffers &pb);
+size_t PassBufferBytes(long long n, int depthSlots, bool vol, bool aov = false);
+void CarvePassBuffers(void *base, long long n, int depthSlots, bool vol, PassBuffers &pb, bool aov = false);
 
 cudaError_t LaunchGenerate(const RenderSceneDev &rs, const PassBuffers &pb, int nPixels, int width, int nActive,
                            int firstSample, int sampleStride, cudaStream_t stream);
@@ -71,6 +76,12 @@ cudaError_t LaunchResolveShadows(const PassBuffers &pb, int depth, int nActive, 
 cudaError_t LaunchFinish(const RenderSceneDev &rs, const PassBuffers &pb, int nActive, cudaStream_t stream);
 cudaError_t LaunchFilmAdd(const PassBuffers &pb, int nPixels, int nSamplesInPass, double *film, cudaStream_t stream);
 // spectral film: the bucket planes behind the 4 * nPixels rgbw doubles of `film`
+// GBufferFilm (film_type 2): the AOV planes behind the bucket planes, and the ids of the last sample of each pixel
+cudaError_t LaunchFilmAddGBuffer(const FilmDev &film, const PassBuffers &pb, int nPixels, int nSamplesInPass, double *acc,
+                                 float *ids, const int32_t *materialIds, cudaStream_t stream);
+// GBufferFilm::GetImage (film.cpp:743-1044): `channels` (B200PT_GBUFFER_*) in the reference's channel order
+cudaError_t LaunchFilmGBufferImage(const FilmDev &film, const double *acc, const float *ids, int nPixels, uint32_t channels,
+                                   int nChannels, float *out, cudaStream_t stream);
 cudaError_t LaunchFilmAddSpectral(const FilmDev &film, const PassBuffers &pb, int nPixels, int nSamplesInPass,
                                   double *acc, cudaStream_t stream);
 cudaError_t LaunchFilmSpectralImage(const FilmDev &film, const double *acc, int nPixels, float *out,

@@ -376,6 +376,11 @@ B2_SPECTRAL_LOOP
     Bsdf bsdf = MakeBsdf<MAT>(rs, mat, LambdaIter(p.lambdaU).lam, p);
     // regularize first: it can turn a specular lobe glossy, which changes Flags() (cpu/integrators.cpp:714-718)
     if (rs.integrator.regularize && (p.flags & PF_ANY_NONSPECULAR)) BsdfRegularize(bsdf);
+    // the film's VisibleSurface (film.cpp:197-213) at the first vertex with a BSDF (cpu/integrators.cpp:721-732): p, the
+    // geometric and the shading normal turned to wo, the material and the instance (GBufferFilm's AOVs)
+    if (p.depth == 0)
+        io.VisibleSurface(Mid(si.pi), DotN(si.n, si.wo) < 0 ? -si.n : si.n, DotN(si.ns, si.wo) < 0 ? -si.ns : si.ns,
+                          mesh.material, (int)hit[5]);
     uint32_t bflags = BsdfFlags(bsdf);
     if (bsdf.type == MAT_DIFFUSE) {  // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
         bool anyR = false;

@@ -90,7 +90,7 @@ struct CameraDev {
 };
 
 struct FilmDev {
-    uint32_t type;               // 0 = RGBFilm (film.h:232-310), 1 = SpectralFilm (film.h:430-560)
+    uint32_t type;               // 0 = RGBFilm (film.h:232-310), 1 = SpectralFilm (film.h:430-560), 2 = GBufferFilm (film.h:322-408)
     int32_t nBuckets;            // spectral film
     int32_t x0, y0, x1, y1;      // pixelBounds
     int32_t fullResX, fullResY;
@@ -100,6 +100,8 @@ struct FilmDev {
     float maxComponentValue;
     float outputRGBFromSensorRGB[9];
     int32_t sensorSpectrum[3];   // r_bar, g_bar, b_bar tables
+    // GBufferFilm: render space -> the AOVs' output space (points through outM; normals through the transpose of outMInv)
+    float outM[16], outMInv[16];
 };
 
 struct SamplerDev {
@@ -140,6 +142,7 @@ struct RenderSceneDev {
     uint32_t nMedia;
     uint32_t geomExt;         // some mesh is a bilinear patch mesh or has per-corner attributes (else the EXT = 0 kernels run)
     const float *cornerAttr;  // per-corner normals / uv of the meshes that have them (MeshAttrDev::nOff, uvOff)
+    const int32_t *materialIds;  // GBufferFilm: the host's Material::materialId per material (materials.cpp:738), or null
 };
 
 // Per-path state, structure of arrays over `n` paths of a pass.  Spectral arrays are [k][path].

@@ -54,7 +54,7 @@ class RenderScene:
     def n_buckets(self):
         """Bands of a spectral film, 0 for an RGB film."""
         d = self.d
-        return int(d["film_spectral"][0]) if "film_type" in d and int(d["film_type"][0]) == 1 else 0
+        return int(d["film_spectral"][0]) if "film_type" in d and int(d["film_type"][0]) in (1, 2) else 0
 
     @property
     def spp(self):
@@ -95,7 +95,13 @@ class RenderScene:
             r.camera_from_raster[:] = [float(x) for x in d["camera_from_raster"]]
             r.lens_radius, r.focal_distance = float(d["camera_params"][0]), float(d["camera_params"][1])
         r.film_type = int(d["film_type"][0]) if "film_type" in d else 0
-        if r.film_type == 1:  # SpectralFilm
+        if r.film_type == 2:  # GBufferFilm: output transform of the AOVs, the host's material ids
+            r.gbuffer_output_from_render[:] = [float(x) for x in d["gbuffer_from_render"].reshape(-1)]
+            r.gbuffer_output_from_render_inv[:] = [float(x) for x in d["gbuffer_from_render_inv"].reshape(-1)]
+            ids = np.ascontiguousarray(d["material_ids"], np.int32)
+            keep.append(ids)
+            r.material_ids = ids.ctypes.data_as(C.POINTER(C.c_int32))
+        if r.film_type in (1, 2):  # SpectralFilm / GBufferFilm buckets
             r.n_buckets = int(d["film_spectral"][0])
             r.lambda_min, r.lambda_max = float(d["film_spectral"][1]), float(d["film_spectral"][2])
         r.pixel_bounds[:] = [int(x) for x in d["film_ints"][:4]]
@@ -237,18 +243,29 @@ class B200Renderer:
     def film_all(self):
         """-> (rgbw (H, W, 4), bucketSums (nB, H, W), weightSums (nB, H, W)); the last two None for an RGB film."""
         nb, n = self.rscene.n_buckets, self.height * self.width
-        buf = np.empty(n * (4 + 2 * nb), dtype=np.float64)
+        d = self.rscene.d
+        extra = 17 if "film_type" in d and int(d["film_type"][0]) == 2 else 0  # GBufferFilm's AOV planes (kGBufferPlanes)
+        buf = np.empty(n * (4 + 2 * nb + extra), dtype=np.float64)
         capi.check(self._L.b200pt_film_read(self._r, buf.ctypes.data_as(C.POINTER(C.c_double))), self.agg._ctx)
         rgbw = buf[:4 * n].reshape(self.height, self.width, 4)
         if not nb:
             return rgbw, None, None
-        planes = buf[4 * n:].reshape(2, nb, self.height, self.width)
+        planes = buf[4 * n:(4 + 2 * nb) * n].reshape(2, nb, self.height, self.width)
         return rgbw, planes[0], planes[1]
 
     def spectral_image(self):
         """The S0.* channels of SpectralFilm::GetImage as (H, W, nB) float32."""
         out = np.empty((self.height, self.width, self.rscene.n_buckets), dtype=np.float32)
         capi.check(self._L.b200pt_film_spectral_image(self._r, out.ctypes.data_as(C.POINTER(C.c_float))), self.agg._ctx)
+        return out
+
+    def gbuffer_image(self, channels=capi.GBUFFER_RADIANCE):
+        """GBufferFilm::GetImage: (H, W, C) float32, R G B then the groups of `channels` in the reference's order."""
+        nc = C.c_int32(0)
+        capi.check(self._L.b200pt_film_gbuffer_image(self._r, int(channels), None, C.byref(nc)), self.agg._ctx)
+        out = np.empty((self.height, self.width, nc.value), np.float32)
+        capi.check(self._L.b200pt_film_gbuffer_image(self._r, int(channels), out.ctypes.data_as(C.POINTER(C.c_float)),
+                                                     C.byref(nc)), self.agg._ctx)
         return out
 
     def film_device_ptr(self):

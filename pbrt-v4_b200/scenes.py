@@ -357,6 +357,19 @@ MATERIALS = {
 }
 
 
+# GBufferFilm, the ISET spectral film (film.cpp:1053-1106): 31 radiance channels + the AOV groups built here; the
+# channel order of its image is R G B, Radiance.C01-31, P.X-Z, MaterialId, InstanceId, Ns.X-Z, N.X-Z, Variance.R-B,
+# RelativeVariance.R-B (film.cpp:766-831)
+GBUFFER_ALL = 1 | 2 | 4 | 8 | 16 | 32 | 64 | 128
+
+
+def _gbuffer_film(out, xres, yres):
+    return (f'Film "gbuffer" "string filename" "{os.path.splitext(out)[0]}.exr" "integer xresolution" {xres} '
+            f'"integer yresolution" {yres} "bool savefp16" false "bool saveRadiance" true "bool saveDepth" true '
+            '"bool saveMaterial" true "bool saveInstance" true "bool saveNormal" true "bool saveNs" true '
+            '"bool saveVariance" true "bool saveRelativeVariance" true')
+
+
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
                  boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
                  film="rgb", nbuckets=31, patches=False, smooth=False, alpha=False):
@@ -375,6 +388,7 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
         'PixelFilter "box"',
         (f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false'
          if film == "rgb" else
+         _gbuffer_film(out, res, res) if film == "gbuffer" else
          # SpectralFilm (film.h:430-560) only accepts an .exr name; the oracle reads its Image out directly
          f'Film "spectral" "string filename" "{os.path.splitext(out)[0]}.exr" "integer nbuckets" {nbuckets} '
          f'"integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false'),
@@ -765,6 +779,7 @@ def config4_pbrt(path, res=1024, spp=256, maxdepth=5, out="config4.exr", seed=0,
         'PixelFilter "box"',
         (f'Film "spectral" "string filename" "{os.path.splitext(out)[0]}.exr" "integer nbuckets" {nbuckets} '
          f'"integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false' if film == "spectral" else
+         _gbuffer_film(out, res, res) if film == "gbuffer" else
          f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} '
          '"bool savefp16" false') + cropw,
         'WorldBegin',

@@ -68,6 +68,9 @@ RENDER_CASES = {
     "cornell_infinite_power_r48_s8": dict(res=48, spp=8, maxdepth=4, lightsampler="power", infinite=(0.4, 0.5, 0.8)),
     # SpectralFilm, 31 bands (configs[3]'s film); the reference image has 3 + 31 channels
     "cornell_spectral_r48_s16": dict(res=48, spp=16, maxdepth=5, film="spectral", nbuckets=31),
+    # GBufferFilm (the ISET film): RGB + 31 radiance channels + position / ids / normals / variance AOVs, on the
+    # instanced Cornell box with smooth-shaded meshes (shading normals differ from the geometric ones, instance ids)
+    "cornell_gbuffer_r48_s16": dict(res=48, spp=16, maxdepth=5, film="gbuffer", smooth="instanced"),
     "cornell_coated_r64_s16": dict(res=64, spp=16, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough")),
     "cornell_glass_r64_s16": dict(res=64, spp=16, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass")),
     # bilinear patch meshes shaded (BilinearPatch::InteractionFromIntersection), one under ReverseOrientation
@@ -223,7 +226,7 @@ def make_render_goldens(P, refrun, out):
         with tempfile.TemporaryDirectory() as tmp:
             pbrt, pfm = os.path.join(tmp, name + ".pbrt"), os.path.join(tmp, name + ".pfm")
             P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
-            if kw.get("film") == "spectral":  # no EXR writer in the oracle build: Film::GetImage read directly
+            if kw.get("film") in ("spectral", "gbuffer"):  # no EXR writer in the oracle build: Film::GetImage read directly
                 img, _, secs = refrun.render_channels(pbrt)
             else:
                 img, secs = refrun.render(pbrt, pfm)

@@ -48,6 +48,7 @@ struct HostIO {
     float shTMax;
     float Beta(int k) const { return beta[k]; }
     void SetBeta(int k, float v) { beta[k] = v; }
+    void VisibleSurface(V3, V3, V3, int, int) {}
     void AddL(int k, float v) { L[k] += v; }
     void ShadowBegin() {}
     void SetLd(int k, float v) { Ld[k] = v; }

@@ -283,3 +283,39 @@ def test_tight_noise_gate(P, name):
     assert np.all(film[..., 3] == rsc.spp)
     assert rrmse(img, ref) <= 1.25 * floor, (rrmse(img, ref), floor)
     assert abs(img.mean() - ref.mean()) <= 0.01 * ref.mean(), (img.mean(), ref.mean())
+
+
+def test_gbuffer_film_matches_reference(P):
+    """GBufferFilm, the ISET spectral film (film.cpp:597-666, 743-1044): every channel of the
+    reference's Film::GetImage - R G B, Radiance.C01-31, P, MaterialId, InstanceId, Ns, N, Variance, RelativeVariance -
+    on the instanced, smooth-shaded Cornell box (16 spp, path for path).  Image channels within rRMSE 1e-3 of the
+    reference's; the id channels equal where the reference's are determinate (this box is closed: everywhere)."""
+    name = "cornell_gbuffer_r48_s16"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    assert ref.shape[-1] == 3 + 31 + 3 + 1 + 1 + 3 + 3 + 3 + 3
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img = r.gbuffer_image(P.scenes.GBUFFER_ALL)
+        rad = r.gbuffer_image()  # the film's default channels: R G B + Radiance
+        # two stripes into one film give the same sums (what the multi-GPU reduce adds up)
+        r.clear()
+        r.render(0, rsc.spp // 2, 2)
+        r.render(1, rsc.spp // 2, 2)
+        striped = r.gbuffer_image(P.scenes.GBUFFER_ALL)
+    finally:
+        r.close()
+    assert img.shape == ref.shape and rad.shape[-1] == 34
+    np.testing.assert_array_equal(rad, img[..., :34])
+    groups = {"rgb": slice(0, 3), "radiance": slice(3, 34), "position": slice(34, 37), "ns": slice(39, 42),
+              "n": slice(42, 45), "variance": slice(45, 48), "relative_variance": slice(48, 51)}
+    for g, sl in groups.items():
+        a, b = img[..., sl].astype(np.float64), ref[..., sl].astype(np.float64)
+        err = np.sqrt(np.mean((a - b) ** 2)) / max(np.mean(np.abs(b)), 1e-12)
+        assert err <= 1e-3, (g, err)
+    np.testing.assert_array_equal(img[..., 37], ref[..., 37])  # MaterialId
+    np.testing.assert_array_equal(img[..., 38], ref[..., 38])  # InstanceId
+    assert len(np.unique(ref[..., 37])) > 3 and ref[..., 38].max() >= 2
+    np.testing.assert_allclose(striped[..., :37], img[..., :37], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(striped[..., 39:], img[..., 39:], rtol=2e-4, atol=1e-5)
