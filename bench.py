@@ -189,13 +189,15 @@ def image_parity(img, ref, ref2=None):
     return out
 
 
-def gpu_image_of_tables(P, tables, local, stream, spectral=False):
+def gpu_image_of_tables(P, tables, local, stream, spectral=False, gbuffer=False):
     """One frame of the scene tables a host adaptor handed over (here: the reference's own dump of the very file the
     reference rendered), all of its samples, on this rank's GPU."""
     rsc = P.RenderScene(tables)
     r = P.B200Renderer(rsc, device=local, stream=stream.cuda_stream)
     try:
         r.render()
+        if gbuffer:
+            return r.gbuffer_image(P.scenes.GBUFFER_ALL)
         if spectral:
             return np.concatenate([r.image(), r.spectral_image()], axis=-1)
         return r.image()
@@ -521,20 +523,27 @@ CONFIG4_CASE = "config4_full"  # BASELINE.json configs[3]; tables in tests/golde
 
 
 def config4_section(args, P, torch, dist, rank, world, local, stream, barrier):
-    """Config 4 end to end: RealisticCamera rays through the lens table, path tracing, 31-band SpectralFilm;
-    --config4-spp of its 256 spp per step, sample stripes over the ranks, the whole film (RGB sums + 2 x 31
-    bucket planes, fp64) reduced by NCCL, the spectral image read back on rank 0."""
+    """Config 4 end to end: RealisticCamera rays through the lens table, path tracing, the ISET GBufferFilm (RGB + 31
+    radiance channels); --config4-spp of its 256 spp per step, sample stripes over the ranks, the film's RGB
+    sums + 31 radiance planes (fp64) reduced by NCCL, the 34-channel image read back into pinned memory on rank 0."""
     rsc = P.RenderScene.load(os.path.join(ROOT, "tests", "golden", CONFIG4_CASE + ".b2rs"))
     spp = min(args.config4_spp, rsc.spp)
     r = P.B200Renderer(rsc, device=local, stream=stream.cuda_stream)
     ptr, nd = r.film_device_ptr()
     film_t = torch.as_tensor(_DevArray(ptr, nd, "<f8"), device="cuda")
+    w, h = rsc.resolution
+    gbuffer = int(rsc.d["film_type"][0]) == 2
+    # the image this frame delivers needs the RGB sums and the radiance planes; the AOV planes behind them stay local
+    film_used = film_t[:w * h * (4 + rsc.n_buckets)] if gbuffer else film_t
+    pinned = torch.empty((h, w, 3 + rsc.n_buckets if gbuffer else rsc.n_buckets), dtype=torch.float32).pin_memory()
 
     def frame(read):
         r.clear()
         r.render(*P.parallel.sample_stripe(spp, rank, world))
-        P.parallel.reduce_film(film_t, dist)
-        return r.spectral_image() if (read and rank == 0) else None
+        P.parallel.reduce_film(film_used, dist)
+        if not (read and rank == 0):
+            return None
+        return r.gbuffer_image(out=pinned.numpy()) if gbuffer else r.spectral_image()
 
     for _ in range(min(args.warmup, 3)):
         frame(False)
@@ -559,16 +568,15 @@ def config4_section(args, P, torch, dist, rank, world, local, stream, barrier):
     dev_ms, e2e_s = (float(x) for x in t.cpu())
     if rank != 0:
         return None
-    w, h = rsc.resolution
     ns = w * h * spp * args.steps
     out = {"metric": "render_msamples_per_s", "unit": "Msamples/s", "value": ns / (dev_ms * 1e-3) * 1e-6,
            "ms_per_frame": dev_ms / args.steps, "scaling": "strong",
            "workload": f"config4: Cornell room + 24-patch spectral chart, realistic camera ({len(rsc.d['camera_lens'])} lens "
-                       f"interfaces, double-Gauss 50 mm), spectral film {rsc.n_buckets} bands, {w}x{h}; {spp} of the frame's "
+                       f"interfaces, double-Gauss 50 mm), {'gbuffer' if gbuffer else 'spectral'} film {rsc.n_buckets} bands, {w}x{h}; {spp} of the frame's "
                        f"{rsc.spp} spp per step, path maxdepth 5; sample stripes over {world} rank(s), film reduced by NCCL",
            "e2e": {"value": ns / e2e_s * 1e-6, "unit": "Msamples/s", "h2d_bytes_per_step": 0,
-                   "d2h_bytes_per_step": w * h * 4 * rsc.n_buckets},
-           "film_bytes_reduced": nd * 8,
+                   "d2h_bytes_per_step": int(pinned.numel()) * 4},
+           "film_bytes_reduced": int(film_used.numel()) * 8,
            "rays_per_frame": (st["closest_rays"] + st["shadow_rays"]) * world,
            "launches_per_frame": st["kernel_launches"], "image_mean": float(img.mean())}
     if not args.no_cpu_baseline:
@@ -589,12 +597,20 @@ def config4_cpu_reference(args, P, local, stream):
     kw = dict(make_golden.CONFIG4_FULL, spp=args.config4_cpu_spp)
     with tempfile.TemporaryDirectory() as tmp:
         pbrt = os.path.join(tmp, "c4.pbrt")
-        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), **kw)
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), film="gbuffer", **kw)
         ref, _, secs = refrun.render_channels(pbrt)
         tables = P.scenes.load_b2rs(refrun.dump_scene(pbrt, os.path.join(tmp, "c4.b2rs")))
-    # path for path (no smooth dielectric in this scene): RGB + the 31 band channels
-    parity = image_parity(gpu_image_of_tables(P, tables, local, stream, spectral=True), ref)
-    parity["sample"] = f"{kw['res']}x{kw['res']}, {kw['spp']} spp, RGB + {ref.shape[-1] - 3} band channels"
+    # path for path (no smooth dielectric in this scene): R G B + Radiance.C01-31 of GBufferFilm::GetImage, and its AOVs
+    img = gpu_image_of_tables(P, tables, local, stream, gbuffer=True)
+    parity = image_parity(img[..., :34], ref[..., :34])
+    aov = {"position": slice(34, 37), "ns": slice(39, 42), "n": slice(42, 45), "variance": slice(45, 48)}
+    parity["aov_rrmse"] = {k: float(np.sqrt(np.mean((img[..., s].astype(np.float64) - ref[..., s]) ** 2)) /
+                                    max(float(np.mean(np.abs(ref[..., s]))), 1e-12)) for k, s in aov.items()}
+    parity["id_mismatches"] = int((img[..., 37:39] != ref[..., 37:39]).sum())
+    # (the variance is a second moment of 4 samples: it doubles the image's own rRMSE; positions and normals are exact)
+    parity["pass"] = bool(parity["pass"] and max(v for k, v in parity["aov_rrmse"].items() if k != "variance") <= 1e-3 and
+                          parity["aov_rrmse"]["variance"] <= 5e-3)
+    parity["sample"] = f"{kw['res']}x{kw['res']}, {kw['spp']} spp, R G B + 31 radiance channels; AOV groups apart"
     n = kw["res"] * kw["res"] * kw["spp"]
     return {"value": n / secs * 1e-6, "parity": parity, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
             "seconds": secs,

@@ -384,6 +384,8 @@ int b200pt_film_clear(b200pt_render *r);
  * planes of bucketSums and n_buckets planes of weightSums, n_pixels doubles each (SpectralFilm::Pixel,
  * film.h:547-556): n_doubles = n_pixels * (4 + 2 * n_buckets).  device_ptr: for an in-place NCCL reduction
  * by the host; film_read copies all n_doubles. */
+/* (GBufferFilm: n_pixels x {4 RGB doubles}, then planes of n_pixels doubles: 31 radiance buckets, 17 AOV sums - a
+ * reduction that only needs R G B + Radiance can stop after the first 4 + 31 planes) */
 int b200pt_film_device_ptr(b200pt_render *r, void **ptr, uint64_t *n_doubles);
 int b200pt_film_read(b200pt_render *r, double *rgb_weight);
 /* spectral film only: the S0.* channels of SpectralFilm::GetImage (film.cpp:1221-1273), n_buckets floats per

@@ -682,7 +682,7 @@ __global__ void FilmAddSpectralKernel(FilmDev fd, PassBuffers pb, int nPixels, i
         SpectralFilmAdd(fd, pb.scalars[path], 1.f, [&](int k) { return cw * L[k * n]; },
                         [&](int b, float v, float w) {
                             bucketSums[(long long)b * nPixels] += v;
-                            weightSums[(long long)b * nPixels] += w;
+                            if (fd.type == 1) weightSums[(long long)b * nPixels] += w;  // (GBufferFilm never reads them)
                         });
     }
 }
@@ -695,7 +695,7 @@ __global__ void FilmAddGBufferKernel(FilmDev fd, PassBuffers pb, int nPixels, in
                                      const int32_t *materialIds) {
     int pix = blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= nPixels) return;
-    double *g = film + (4ll + 2ll * fd.nBuckets) * nPixels + pix;  // plane q at g[q * nPixels]
+    double *g = film + (4ll + fd.nBuckets) * nPixels + pix;  // plane q at g[q * nPixels] (no weightSums planes in this film)
     const long long n = pb.n, P = nPixels;
     const float *M = fd.outM, *I = fd.outMInv;
     double acc[kGBufferPlanes];
@@ -727,11 +727,15 @@ __global__ void FilmAddGBufferKernel(FilmDev fd, PassBuffers pb, int nPixels, in
             }
             acc[16] += 1;
         }
-        // p.materialId = visibleSurface->materialId: every sample writes it; a sample without a VisibleSurface leaves
-        // what a default-constructed one holds (indeterminate in the reference; 0 here)
-        const int mi = a[0] != 0.f ? (int)a[10 * n] : -1;
-        idM = mi < 0 ? 0.f : (materialIds ? (float)materialIds[mi] : (float)(mi + 1));
-        idI = a[0] != 0.f ? a[11 * n] : 0.f;
+        // p.materialId = visibleSurface->materialId: every sample writes it.  A sample without a VisibleSurface (no camera
+        // ray through the lens, an escaped ray) hands the film a default-constructed one whose ids are never initialised
+        // (film.h:155-156): in the CPU build that is the stack slot of the previous sample's, so the ids of the last
+        // sample that HAD a surface stay - which is what is kept here (within the pixel; 0 before the first)
+        if (a[0] != 0.f) {
+            const int mi = (int)a[10 * n];
+            idM = mi < 0 ? 0.f : (materialIds ? (float)materialIds[mi] : (float)(mi + 1));
+            idI = a[11 * n];
+        }
     }
     for (int q = 0; q < kGBufferPlanes; ++q) g[q * P] = acc[q];
     ids[pix] = idM;
@@ -760,7 +764,7 @@ __global__ void FilmGBufferImageKernel(FilmDev film, const double *acc, const fl
             float L = (float)acc[(4ll + k) * P + pix];
             o[c++] = w != 0 ? L / w : L;
         }
-    const double *gq = acc + (4ll + 2ll * film.nBuckets) * P + pix;
+    const double *gq = acc + (4ll + film.nBuckets) * P + pix;
     const float gw = (float)gq[0];
     if (channels & B200PT_GBUFFER_POSITION)
         for (int k = 0; k < 3; ++k) {

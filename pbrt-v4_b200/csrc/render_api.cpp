@@ -158,7 +158,10 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         }
     }
     if (const char *v = getenv("B200PT_PASS_PATHS")) r->maxPathsPerPass = std::max(1ll, atoll(v));
-    r->filmDoubles = size_t(r->nPixels) * (4 + 2 * size_t(r->dev.film.nBuckets) + (r->dev.film.type == 2 ? kGBufferPlanes : 0));
+    // RGBFilm: {rgbSum[3], weightSum}; SpectralFilm: + bucketSums and weightSums planes; GBufferFilm: + the 31 radiance
+    // planes (its image divides by the RGB weight sum, film.cpp:846-850: no per-bucket weights) + the AOV planes
+    r->filmDoubles = size_t(r->nPixels) * (r->dev.film.type == 2 ? 4 + size_t(r->dev.film.nBuckets) + kGBufferPlanes
+                                                                 : 4 + 2 * size_t(r->dev.film.nBuckets));
     if (r->dev.film.type == 2 &&
         (cudaMalloc((void **)&r->dFilmIds, sizeof(float) * 2 * size_t(r->nPixels)) != cudaSuccess ||
          cudaMemsetAsync(r->dFilmIds, 0, sizeof(float) * 2 * size_t(r->nPixels), ctx->stream) != cudaSuccess)) {

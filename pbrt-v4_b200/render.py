@@ -244,12 +244,14 @@ class B200Renderer:
         """-> (rgbw (H, W, 4), bucketSums (nB, H, W), weightSums (nB, H, W)); the last two None for an RGB film."""
         nb, n = self.rscene.n_buckets, self.height * self.width
         d = self.rscene.d
-        extra = 17 if "film_type" in d and int(d["film_type"][0]) == 2 else 0  # GBufferFilm's AOV planes (kGBufferPlanes)
-        buf = np.empty(n * (4 + 2 * nb + extra), dtype=np.float64)
+        gb = "film_type" in d and int(d["film_type"][0]) == 2  # GBufferFilm: 31 radiance planes + 17 AOV planes (kGBufferPlanes)
+        buf = np.empty(n * (4 + nb + 17 if gb else 4 + 2 * nb), dtype=np.float64)
         capi.check(self._L.b200pt_film_read(self._r, buf.ctypes.data_as(C.POINTER(C.c_double))), self.agg._ctx)
         rgbw = buf[:4 * n].reshape(self.height, self.width, 4)
         if not nb:
             return rgbw, None, None
+        if gb:
+            return rgbw, buf[4 * n:(4 + nb) * n].reshape(nb, self.height, self.width), None
         planes = buf[4 * n:(4 + 2 * nb) * n].reshape(2, nb, self.height, self.width)
         return rgbw, planes[0], planes[1]
 
@@ -259,11 +261,14 @@ class B200Renderer:
         capi.check(self._L.b200pt_film_spectral_image(self._r, out.ctypes.data_as(C.POINTER(C.c_float))), self.agg._ctx)
         return out
 
-    def gbuffer_image(self, channels=capi.GBUFFER_RADIANCE):
-        """GBufferFilm::GetImage: (H, W, C) float32, R G B then the groups of `channels` in the reference's order."""
+    def gbuffer_image(self, channels=capi.GBUFFER_RADIANCE, out=None):
+        """GBufferFilm::GetImage: (H, W, C) float32, R G B then the groups of `channels` in the reference's order.
+        out: optional float32 array of that shape to fill (e.g. pinned host memory: the copy then runs at PCIe speed)."""
         nc = C.c_int32(0)
         capi.check(self._L.b200pt_film_gbuffer_image(self._r, int(channels), None, C.byref(nc)), self.agg._ctx)
-        out = np.empty((self.height, self.width, nc.value), np.float32)
+        if out is None:
+            out = np.empty((self.height, self.width, nc.value), np.float32)
+        assert out.dtype == np.float32 and out.size == self.height * self.width * nc.value and out.flags.c_contiguous
         capi.check(self._L.b200pt_film_gbuffer_image(self._r, int(channels), out.ctypes.data_as(C.POINTER(C.c_float)),
                                                      C.byref(nc)), self.agg._ctx)
         return out

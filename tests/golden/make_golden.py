@@ -125,8 +125,15 @@ def make_config4_goldens(P, refrun, out):
     import tempfile
     with tempfile.TemporaryDirectory() as tmp:
         pbrt = os.path.join(tmp, "c4.pbrt")
-        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), **CONFIG4_FULL)
+        # config 4 is quoted on Film "gbuffer" (SURVEY 8d): full-size tables with that film for bench.py; the spectral film
+        # keeps its miniature below, the gbuffer film gets one of its own
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), film="gbuffer", **CONFIG4_FULL)
         refrun.dump_scene(pbrt, os.path.join(out, "config4_full.b2rs"))
+        P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), film="gbuffer", **CONFIG4_SMALL)
+        refrun.dump_scene(pbrt, os.path.join(out, "config4_gbuffer_small.b2rs"))
+        img, names, secs = refrun.render_channels(pbrt)
+        np.save(os.path.join(out, "config4_gbuffer_small_ref.npy"), img.astype(np.float32))
+        print("config4_gbuffer_small", img.shape, "mean", img[..., :3].mean(axis=(0, 1)), f"{secs:.2f}s")
         P.scenes.config4_pbrt(pbrt, out=os.path.join(tmp, "c4.exr"), **CONFIG4_SMALL)
         refrun.dump_scene(pbrt, os.path.join(out, "config4_small.b2rs"))
         img, names, secs = refrun.render_channels(pbrt)
