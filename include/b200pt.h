@@ -141,7 +141,9 @@ typedef struct b200pt_trace_stats {
     uint64_t nodes_visited;
     uint64_t leaves_visited;
     uint64_t prims_tested;
-    float kernel_ms; /* CUDA-event time of the traversal kernel(s) of the last call */
+    float kernel_ms; /* CUDA-event time of the traversal kernel(s) of the last call (B200PT_MEM_DEVICE); for a
+                      * host-buffer call: first launch to last launch of the chunk pipeline, which includes waits on
+                      * the copies in */
     /* 8-wide nodes fetched (256 B each; nodes_visited counts their 8 box tests each) and rays that went through
      * the exact binary kernel instead (non-finite 1/d or origin, at the top level or inside an instance) */
     uint64_t wide_nodes_visited;
@@ -169,10 +171,10 @@ int b200pt_scene_destroy(b200pt_scene *scene);
 int b200pt_scene_bounds(const b200pt_scene *scene, float bounds_min_max[6]);
 int b200pt_scene_get_stats(const b200pt_scene *scene, b200pt_scene_stats *out);
 
-/* rays: n x 7 floats {o.xyz, d.xyz, tMax}; hits: n records; occluded: n bytes (0/1).
- * mem: B200PT_MEM_HOST (copied through pinned staging inside the call, the call
- * returns after the results are in `hits`) or B200PT_MEM_DEVICE (asynchronous on
- * the context's stream), optionally or-ed with B200PT_TRACE_COUNTERS. */
+/* rays: n x 7 floats {o.xyz, d.xyz, tMax}; hits: n records; occluded: n bytes (0/1); n <= 2^31 - 2^22.
+ * mem: B200PT_MEM_HOST (copied straight from / to the caller's memory in 2^21-ray chunks over three streams - the
+ * copies overlap the traversal only when that memory is pinned; the call returns after the results are in `hits`)
+ * or B200PT_MEM_DEVICE (asynchronous on the context's stream), optionally or-ed with B200PT_TRACE_COUNTERS. */
 int b200pt_intersect_closest(b200pt_scene *scene, const float *rays, int64_t n,
                              b200pt_hit *hits, uint32_t mem);
 int b200pt_intersect_any(b200pt_scene *scene, const float *rays, int64_t n,
@@ -361,7 +363,12 @@ typedef struct b200pt_render_desc {
     float gbuffer_output_from_render[16];
     float gbuffer_output_from_render_inv[16];
     const int32_t *material_ids;
+    /* the film's pixel filter (filters.h): only B200PT_FILTER_BOX (BoxFilter, filters.h:37-77, radius = filter_radius:
+     * uniform sample offsets, weight 1) is implemented; any other value is refused with B200PT_ERR_INVALID - pbrt's
+     * default is the Gaussian, a host adaptor must say so instead of getting a box-filtered image silently. */
+    uint32_t filter_type;
 } b200pt_render_desc;
+enum { B200PT_FILTER_BOX = 0, B200PT_FILTER_GAUSSIAN = 1, B200PT_FILTER_MITCHELL = 2, B200PT_FILTER_SINC = 3, B200PT_FILTER_TRIANGLE = 4 };
 
 typedef struct b200pt_render b200pt_render;
 
@@ -370,6 +377,10 @@ typedef struct b200pt_render_stats {
     uint64_t closest_rays, shadow_rays;
     uint32_t kernel_launches;
     float gpu_ms;            /* CUDA-event time of the last run */
+    /* volpath only: paths still alive when a pass stopped after its 96 wavefront iterations, and light-sample walks
+     * still crossing interfaces after 64 segments - both are dropped there (the reference's loops are bounded by
+     * maxdepth and roulette only); non-zero counts mean the image is darker than the reference's */
+    uint64_t vol_paths_cut, vol_walks_cut;
 } b200pt_render_stats;
 
 int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b200pt_render **out);

@@ -232,7 +232,10 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
     auto dumpFilm = [&](const auto *rf) {
         Bounds2i pb = rf->pixelBounds;
         w.i32("film_ints", {6}, {pb.pMin.x, pb.pMin.y, pb.pMax.x, pb.pMax.y, rf->fullResolution.x, rf->fullResolution.y});
-        if (!rf->filter.template Is<BoxFilter>()) die("only the box filter is dumped so far");
+        // filter_type as include/b200pt.h numbers them; the library refuses what it has not got (box only)
+        const uint32_t ft = rf->filter.template Is<BoxFilter>() ? 0u : rf->filter.template Is<GaussianFilter>() ? 1u
+                          : rf->filter.template Is<MitchellFilter>() ? 2u : rf->filter.template Is<LanczosSincFilter>() ? 3u : 4u;
+        w.u32("filter_type", {1}, {ft});
         Vector2f fr = rf->filter.Radius();
         w.f32("film_params", {4}, {fr.x, fr.y, rf->sensor->imagingRatio, rf->maxComponentValue});
         std::vector<float> om(9);

@@ -168,6 +168,9 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         }
     }
     r.film_type = T.at("film_type").u()[0];
+    if (r.film_type == 2)
+        die("pbrt_b200: Film \"gbuffer\" writes EXR only (film.cpp:1081-1083) and the oracle build has no EXR writer "
+            "(oracle/ref.mk); the GBufferFilm path is exercised through libb200pt.so directly (tests/test_render_gpu.py)");
     if (r.film_type == 1) {
         const float *fs = T.at("film_spectral").f();
         r.n_buckets = uint32_t(fs[0]);
@@ -178,6 +181,7 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
     memcpy(r.pixel_bounds, fi, 16);
     memcpy(r.full_resolution, fi + 4, 8);
     const float *fp = T.at("film_params").f();
+    r.filter_type = T.has("filter_type") ? T.at("filter_type").u()[0] : 0;
     r.filter_radius[0] = fp[0];
     r.filter_radius[1] = fp[1];
     r.imaging_ratio = fp[2];

@@ -184,7 +184,7 @@ class RenderDesc(C.Structure):
                 ("microlens_offsets", C.POINTER(C.c_float)), ("microlens_offset_from_sensor", C.c_float),
                 ("microlens_simulation_radius", C.c_int32),
                 ("gbuffer_output_from_render", C.c_float * 16), ("gbuffer_output_from_render_inv", C.c_float * 16),
-                ("material_ids", C.POINTER(C.c_int32))]
+                ("material_ids", C.POINTER(C.c_int32)), ("filter_type", C.c_uint32)]
 
 
 GBUFFER_RADIANCE, GBUFFER_POSITION, GBUFFER_MATERIAL, GBUFFER_INSTANCE = 1, 2, 4, 8
@@ -193,7 +193,8 @@ GBUFFER_NS, GBUFFER_NORMAL, GBUFFER_VARIANCE, GBUFFER_RELATIVE_VARIANCE = 16, 32
 
 class RenderStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
-                ("kernel_launches", C.c_uint32), ("gpu_ms", C.c_float)]
+                ("kernel_launches", C.c_uint32), ("gpu_ms", C.c_float),
+                ("vol_paths_cut", C.c_uint64), ("vol_walks_cut", C.c_uint64)]
 
 
 SYMBOLS.update({

@@ -259,7 +259,21 @@ static int EnsureStaging(b200pt_ctx *ctx, size_t inBytes, size_t outBytes) {
 // Host-buffer batches (B200PT_MEM_HOST) go through in chunks on three streams: while chunk k is traversed, chunk k + 1
 // is on its way in and chunk k - 1 on its way out (PCIe is full duplex), so the call costs about the longest of the
 // three legs instead of their sum.  Chunks are independent ray ranges: results are those of one launch.
+static int IntersectHostPipelinedImpl(b200pt_scene *s, const float *rays, int64_t n, void *out, bool any);
 static int IntersectHostPipelined(b200pt_scene *s, const float *rays, int64_t n, void *out, bool any) {
+    int rc = IntersectHostPipelinedImpl(s, rays, n, out, any);
+    if (rc != B200PT_OK) {
+        // copies against the caller's buffers may still be in flight on the three streams: drain them before the
+        // caller gets its buffers back (and may free them)
+        b200pt_ctx *ctx = s->ctx;
+        if (ctx->sIn) cudaStreamSynchronize(ctx->sIn);
+        cudaStreamSynchronize(ctx->stream);
+        if (ctx->sOut) cudaStreamSynchronize(ctx->sOut);
+        (void)cudaGetLastError();
+    }
+    return rc;
+}
+static int IntersectHostPipelinedImpl(b200pt_scene *s, const float *rays, int64_t n, void *out, bool any) {
     b200pt_ctx *ctx = s->ctx;
     const size_t outRec = any ? 1 : sizeof(b200pt_hit);
     int64_t chunk = 1 << 21;

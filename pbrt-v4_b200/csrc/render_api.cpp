@@ -229,6 +229,7 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
     int *exact = nullptr;
     if (int rc = EnsureExactScratch(ctx, size_t(need), &exact)) return rc;
     int launches = 0;
+    uint64_t volPathsCut = 0, volWalksCut = 0;
     B2_CUDA(ctx, cudaMemsetAsync(r->dCounters, 0, 4 * sizeof(unsigned long long), ctx->stream));
     B2_CUDA(ctx, cudaEventRecord(r->ev0, ctx->stream));
     for (int done = 0; done < n_samples; done += perPass) {
@@ -263,7 +264,8 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                 B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
                 usedIters = j + 1;
                 // the transmittance walks: closest hit of every light-sample ray, one segment, until none goes on
-                for (int live = hc[0], seg = 0; live > 0 && seg < 64; ++seg) {
+                int live = hc[0];
+                for (int seg = 0; live > 0 && seg < 64; ++seg) {
                     B2_CUDA(ctx, cudaMemsetAsync(pb.shContinue, 0, sizeof(int), ctx->stream));
                     B2_CUDA(ctx, LaunchTraversePersist(sc, pb.shRays, hc[0], (b200pt_hit *)pb.shHits, nullptr, false,
                                                        r->dRayCounter, nullptr, ctx->smCount, stackDepth, ctx->refillMin,
@@ -273,7 +275,9 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
                     B2_CUDA(ctx, cudaMemcpyAsync(&live, pb.shContinue, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
                     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
                 }
+                volWalksCut += uint64_t(live);  // walks still crossing interfaces after 64 segments are dropped
                 if (hc[1] == 0) break;
+                if (j == kVolMaxIterations - 1) volPathsCut += uint64_t(hc[1]);  // paths alive at the iteration cap
             }
             B2_CUDA(ctx, LaunchFinish(r->dev, pb, nActive, ctx->stream));
             B2_CUDA(ctx, LaunchFilmAdd(pb, nPix, ns, r->dFilm, ctx->stream));
@@ -325,6 +329,8 @@ int b200pt_render_run(b200pt_render *r, int32_t first_sample, int32_t n_samples,
     r->timed = true;
     r->stats.samples = (uint64_t)n_samples * nPix;
     r->stats.kernel_launches = (uint32_t)launches;
+    r->stats.vol_paths_cut = volPathsCut;
+    r->stats.vol_walks_cut = volWalksCut;
     return B200PT_OK;
 }
 

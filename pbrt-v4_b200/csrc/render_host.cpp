@@ -43,6 +43,8 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("omni camera: microlens simulation radius must be 0..8");
         }
     }
+    if (d->filter_type != B200PT_FILTER_BOX)
+        return bad("unsupported pixel filter: only the box filter is implemented (filter_type)");
     if (d->film_type > 2) return bad("unsupported film type");
     if (d->film_type == 2 && (d->n_buckets != 31 || d->lambda_min != 395.f || d->lambda_max != 705.f))
         return bad("gbuffer film: 31 buckets over 395..705 nm (hard-coded in the reference, film.h:383-389)");

@@ -24,9 +24,10 @@ constexpr int kGBufferPlanes = 17;
 // One pass = nPixels x nSamplesInPass paths; path i is pixel i % nPixels, sample slot i / nPixels.
 // Path state is indexed by path id and laid out [field][path] so a warp's accesses coalesce; the
 // queues (rays, hits, shadow rays, material queues) are dense and indexed by queue slot.  Queue
-// lengths live on the device (counts): the host never reads them inside a pass, launches are sized
-// for the worst case and threads past the length exit (as the reference's wavefront does,
-// wavefront/integrator.cpp:403-406 "maxQueueSize").
+// lengths live on the device (counts): the surface path never reads them on the host inside a pass, launches are
+// sized for the worst case and threads past the length exit (as the reference's wavefront does,
+// wavefront/integrator.cpp:403-406 "maxQueueSize").  The volumetric path reads two lengths per iteration and one per
+// walk segment (render_api.cpp: interface crossings make the iteration count data dependent).
 struct PassBuffers {
     int n;                 // capacity in paths
     // ---- per path

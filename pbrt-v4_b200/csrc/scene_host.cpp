@@ -50,16 +50,24 @@ bool ValidateTree(const HostTree &t, uint32_t nPrims, std::string &err) {
         err = "bvh with no nodes";
         return false;
     }
-    // every node reachable exactly once in DFS order, offsets in range
+    // every node of the array reached exactly once from the root, offsets in range (the flatten and pair-node loops
+    // below walk the whole array: an unreachable node with a garbage offset would index out of bounds there)
     std::vector<uint32_t> stack{0};
+    std::vector<uint8_t> seen(nn, 0);
     uint32_t visited = 0;
     while (!stack.empty()) {
         uint32_t i = stack.back();
         stack.pop_back();
-        if (i >= nn || ++visited > nn) {
+        if (i >= nn) {
             err = "bvh node index out of range";
             return false;
         }
+        if (seen[i]) {
+            err = "bvh node reached twice";
+            return false;
+        }
+        seen[i] = 1;
+        ++visited;
         const Node32 &nd = t.nodes[i];
         if (nd.nPrims > 0) {
             if (nd.offset < 0 || uint64_t(nd.offset) + nd.nPrims > nPrims) {
@@ -74,6 +82,10 @@ bool ValidateTree(const HostTree &t, uint32_t nPrims, std::string &err) {
             stack.push_back(uint32_t(nd.offset));
             stack.push_back(i + 1);
         }
+    }
+    if (visited != nn) {
+        err = "bvh has nodes that are not reachable from its root";
+        return false;
     }
     return true;
 }

@@ -765,7 +765,7 @@ cudaError_t LaunchTraversePersist(const DeviceScene &sc, const float *rays, long
                                   int refillMin, int nodeMin, cudaStream_t stream, bool internalHits,
                                   const int *nDev, int *exactScratch) {
     if (n <= 0) return cudaSuccess;
-    if (n > 0x7fffffffll) return cudaErrorInvalidValue;
+    if (n > 0x7fffffffll - (1ll << 22)) return cudaErrorInvalidValue;  // the fetch counter overshoots n by up to the resident lanes
     if (stackDepth + 4 > kSmemDepth + kLocalDepth) return cudaErrorInvalidValue;  // + the saved parent context of an instance
     const bool wide = exactScratch && sc.wide && int(sc.maxStackWide) + 2 <= kSmemDepth + kLocalDepth;
     TraverseLaunch a{&sc, rays, n, hits, occluded, rayCounter, counters, smCount, refillMin, nodeMin, stream, nDev, nullptr,

@@ -107,6 +107,7 @@ class RenderScene:
         r.pixel_bounds[:] = [int(x) for x in d["film_ints"][:4]]
         r.full_resolution[:] = [int(x) for x in d["film_ints"][4:6]]
         r.filter_radius[:] = [float(x) for x in d["film_params"][:2]]
+        r.filter_type = int(d["filter_type"][0]) if "filter_type" in d else 0  # 0 = box (older dumps: box only)
         r.imaging_ratio, r.max_component_value = float(d["film_params"][2]), float(d["film_params"][3])
         r.output_rgb_from_sensor_rgb[:] = [float(x) for x in d["film_matrix"]]
         r.sensor_spectrum[:] = [int(x) for x in d["film_sensor"]]
