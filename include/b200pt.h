@@ -415,6 +415,13 @@ enum {
     B200PT_GBUFFER_NS = 16, B200PT_GBUFFER_NORMAL = 32, B200PT_GBUFFER_VARIANCE = 64, B200PT_GBUFFER_RELATIVE_VARIANCE = 128
 };
 int b200pt_film_gbuffer_image(b200pt_render *r, uint32_t channels, float *out, int32_t *n_channels);
+/* Film::WriteImage for the .exr case (film.cpp:542-574 -> Image::WriteEXR, util/image.cpp:1008+): the film's image
+ * finalised and packed ON THE DEVICE into the chunks of an uncompressed scanline OpenEXR file, then written to `path`.
+ * RGBFilm: R G B; GBufferFilm: R G B + the groups of `channels` under the reference's channel names ("Radiance.C01" ...,
+ * "P.X", "MaterialId", "Ns.X", ..., film.cpp:752-766); SpectralFilm: R G B + "S0.<lambda>nm" as the reference names them.
+ * fp16 != 0 writes HALF channels (values clamped to 65504 as the reference does), else FLOAT.  dataWindow =
+ * pixel_bounds, displayWindow = full_resolution.  No compression, no metadata beyond the required attributes. */
+int b200pt_film_write_exr(b200pt_render *r, uint32_t channels, const char *path, int32_t fp16);
 int b200pt_render_get_stats(const b200pt_render *r, b200pt_render_stats *out);
 
 /* Host-only: build the binary SAH BVH for one primitive list exactly as the

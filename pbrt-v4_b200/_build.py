@@ -36,6 +36,7 @@ CU_SOURCES = [
     ("render.cu", ["--fmad=false", "-DB2_RENDER_PART=3"], "render_3"),
     ("render.cu", ["--fmad=false", "-DB2_RENDER_PART=4", "-DB2_SPECTRAL_UNROLL=4", "-DB2_VOL_MIN_BLOCKS=4"], "render_4"),
     ("noalloc.cu", []),
+    ("exr_pack.cu", []),
 ]
 
 

@@ -205,6 +205,7 @@ SYMBOLS.update({
     "b200pt_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "b200pt_film_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "b200pt_film_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "b200pt_film_write_exr": (C.c_int, [C.c_void_p, C.c_uint32, C.c_char_p, C.c_int32]),
     "b200pt_film_gbuffer_image": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "b200pt_film_spectral_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "b200pt_render_get_stats": (C.c_int, [C.c_void_p, C.POINTER(RenderStats)]),

@@ -386,6 +386,158 @@ int b200pt_film_gbuffer_image(b200pt_render *r, uint32_t channels, float *out, i
     return B200PT_OK;
 }
 
+int b200pt_film_write_exr(b200pt_render *r, uint32_t channels, const char *path, int32_t fp16) {
+    if (!r || !path) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    const FilmDev &film = r->dev.film;
+    const int W = r->host.width, H = r->host.height, nB = film.nBuckets;
+    // ---- channel names in the order the image kernels write them
+    std::vector<std::string> names = {"R", "G", "B"};
+    auto numbered = [&](const char *prefix, int n) {
+        for (int i = 1; i <= n; ++i) {
+            char b[32];
+            snprintf(b, sizeof b, "%s%02d", prefix, i);
+            names.push_back(b);
+        }
+    };
+    if (film.type == 2) {
+        if (channels & B200PT_GBUFFER_RADIANCE) numbered("Radiance.C", nB);
+        if (channels & B200PT_GBUFFER_POSITION) for (const char *c : {"P.X", "P.Y", "P.Z"}) names.push_back(c);
+        if (channels & B200PT_GBUFFER_MATERIAL) names.push_back("MaterialId");
+        if (channels & B200PT_GBUFFER_INSTANCE) names.push_back("InstanceId");
+        if (channels & B200PT_GBUFFER_NS) for (const char *c : {"Ns.X", "Ns.Y", "Nx.Z"}) names.push_back(c);  // (sic, film.cpp:765)
+        if (channels & B200PT_GBUFFER_NORMAL) for (const char *c : {"N.X", "N.Y", "N.Z"}) names.push_back(c);
+        if (channels & B200PT_GBUFFER_VARIANCE) for (const char *c : {"Variance.R", "Variance.G", "Variance.B"}) names.push_back(c);
+        if (channels & B200PT_GBUFFER_RELATIVE_VARIANCE)
+            for (const char *c : {"RelativeVariance.R", "RelativeVariance.G", "RelativeVariance.B"}) names.push_back(c);
+    } else if (film.type == 1) {
+        for (int i = 0; i < nB; ++i) {  // SpectralFilm::GetImage (film.cpp:1235-1243): bucket centre, '.' written as ','
+            const float t = (i + 0.5f) / nB;
+            float lambda = (1 - t) * 395.f + t * 705.f;  // Lerp(t, lambdaMin, lambdaMax)
+            char b[48];
+            snprintf(b, sizeof b, "S0.%.3fnm", lambda);
+            std::string s = b;
+            std::replace(s.begin() + 3, s.end(), '.', ',');
+            names.push_back(s);
+        }
+    }
+    const int nc = int(names.size());
+    // ---- the float image on the device
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    float *dImg = nullptr;
+    unsigned char *dOut = nullptr, *hOut = nullptr;
+    int *dOrder = nullptr;
+    const size_t px = size_t(W) * H, bytes = fp16 ? 2 : 4;
+    const size_t payload = size_t(H) * (8 + size_t(nc) * W * bytes);
+    auto cleanup = [&]() {
+        cudaFree(dImg);
+        cudaFree(dOut);
+        cudaFree(dOrder);
+        cudaFreeHost(hOut);
+    };
+#define B2_TRY(call)                                                            \
+    do {                                                                        \
+        cudaError_t e_ = (call);                                                \
+        if (e_ != cudaSuccess) {                                                \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);      \
+            cleanup();                                                          \
+            return B200PT_ERR_CUDA;                                             \
+        }                                                                       \
+    } while (0)
+    B2_TRY(cudaMalloc((void **)&dImg, sizeof(float) * px * nc));
+    if (film.type == 2) {
+        B2_TRY(LaunchFilmGBufferImage(film, r->dFilm, r->dFilmIds, r->nPixels, channels, nc, dImg, ctx->stream));
+    } else {
+        // R G B (channels-last, 3 wide) and the buckets (nB wide) side by side into the nc-wide image
+        B2_TRY(LaunchFilmImage(film, r->dFilm, r->nPixels, r->dImage, ctx->stream));
+        B2_TRY(cudaMemcpy2DAsync(dImg, sizeof(float) * nc, r->dImage, sizeof(float) * 3, sizeof(float) * 3, px,
+                                 cudaMemcpyDeviceToDevice, ctx->stream));
+        if (film.type == 1) {
+            B2_TRY(LaunchFilmSpectralImage(film, r->dFilm, r->nPixels, r->dImage, ctx->stream));
+            B2_TRY(cudaMemcpy2DAsync(dImg + 3, sizeof(float) * nc, r->dImage, sizeof(float) * nB, sizeof(float) * nB, px,
+                                     cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+    }
+    // ---- file order = alphabetical (OpenEXR stores the channel list sorted by name)
+    std::vector<int> order(nc);
+    for (int i = 0; i < nc; ++i) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return names[a] < names[b]; });
+    B2_TRY(cudaMalloc((void **)&dOrder, sizeof(int) * nc));
+    B2_TRY(cudaMemcpyAsync(dOrder, order.data(), sizeof(int) * nc, cudaMemcpyHostToDevice, ctx->stream));
+    B2_TRY(cudaMalloc((void **)&dOut, payload));
+    B2_TRY(cudaMallocHost((void **)&hOut, payload));
+    B2_TRY(LaunchExrPack(dImg, W, H, nc, dOrder, fp16 != 0, film.y0, dOut, ctx->stream));
+    B2_TRY(cudaMemcpyAsync(hOut, dOut, payload, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_TRY(cudaStreamSynchronize(ctx->stream));
+#undef B2_TRY
+    // ---- header (OpenEXR file layout: magic, version, attributes, offset table, chunks)
+    std::string h;
+    auto put32 = [&](int32_t v) { h.append(reinterpret_cast<const char *>(&v), 4); };
+    auto putf = [&](float v) { h.append(reinterpret_cast<const char *>(&v), 4); };
+    auto attr = [&](const char *name, const char *type, const std::string &value) {
+        h += name;
+        h.push_back('\0');
+        h += type;
+        h.push_back('\0');
+        put32(int32_t(value.size()));
+        h += value;
+    };
+    put32(20000630);
+    put32(2);
+    {
+        std::string v;
+        for (int c = 0; c < nc; ++c) {
+            v += names[order[c]];
+            v.push_back('\0');
+            int32_t type = fp16 ? 1 : 2, one = 1;
+            v.append(reinterpret_cast<const char *>(&type), 4);
+            v.append(4, '\0');  // pLinear + reserved
+            v.append(reinterpret_cast<const char *>(&one), 4);
+            v.append(reinterpret_cast<const char *>(&one), 4);
+        }
+        v.push_back('\0');
+        attr("channels", "chlist", v);
+    }
+    attr("compression", "compression", std::string(1, '\0'));
+    auto box = [&](int x0, int y0, int x1, int y1) {
+        std::string v;
+        for (int32_t q : {x0, y0, x1, y1}) v.append(reinterpret_cast<const char *>(&q), 4);
+        return v;
+    };
+    attr("dataWindow", "box2i", box(film.x0, film.y0, film.x1 - 1, film.y1 - 1));
+    attr("displayWindow", "box2i", box(0, 0, film.fullResX - 1, film.fullResY - 1));
+    attr("lineOrder", "lineOrder", std::string(1, '\0'));
+    {
+        std::string s = h;
+        h.clear();
+        putf(1.f);
+        std::string one = h;
+        h.clear();
+        putf(0.f);
+        putf(0.f);
+        std::string centre = h;
+        h = s;
+        attr("pixelAspectRatio", "float", one);
+        attr("screenWindowCenter", "v2f", centre);
+        attr("screenWindowWidth", "float", one);
+    }
+    h.push_back('\0');
+    const uint64_t first = h.size() + 8ull * H, lineChunk = 8 + uint64_t(nc) * W * bytes;
+    for (int y = 0; y < H; ++y) {
+        uint64_t off = first + lineChunk * y;
+        h.append(reinterpret_cast<const char *>(&off), 8);
+    }
+    FILE *f = fopen(path, "wb");
+    bool ok = f && fwrite(h.data(), 1, h.size(), f) == h.size() && fwrite(hOut, 1, payload, f) == payload;
+    if (f) ok = (fclose(f) == 0) && ok;
+    cleanup();
+    if (!ok) {
+        ctx->err = std::string("b200pt_film_write_exr: cannot write ") + path;
+        return B200PT_ERR_INVALID;
+    }
+    return B200PT_OK;
+}
+
 int b200pt_film_spectral_image(b200pt_render *r, float *buckets) {
     if (!r || !buckets) return B200PT_ERR_INVALID;
     b200pt_ctx *ctx = r->scene->ctx;

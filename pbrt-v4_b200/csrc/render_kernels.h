@@ -83,6 +83,9 @@ cudaError_t LaunchFilmAddGBuffer(const FilmDev &film, const PassBuffers &pb, int
 // GBufferFilm::GetImage (film.cpp:743-1044): `channels` (B200PT_GBUFFER_*) in the reference's channel order
 cudaError_t LaunchFilmGBufferImage(const FilmDev &film, const double *acc, const float *ids, int nPixels, uint32_t channels,
                                    int nChannels, float *out, cudaStream_t stream);
+// exr_pack.cu: channels-last float image -> scanline chunks of an uncompressed EXR (order[c] = image channel of file channel c)
+cudaError_t LaunchExrPack(const float *img, int width, int height, int nChannels, const int *order, bool half, int y0,
+                          unsigned char *out, cudaStream_t stream);
 cudaError_t LaunchFilmAddSpectral(const FilmDev &film, const PassBuffers &pb, int nPixels, int nSamplesInPass,
                                   double *acc, cudaStream_t stream);
 cudaError_t LaunchFilmSpectralImage(const FilmDev &film, const double *acc, int nPixels, float *out,

@@ -274,6 +274,10 @@ class B200Renderer:
                                                      C.byref(nc)), self.agg._ctx)
         return out
 
+    def write_exr(self, path, channels=capi.GBUFFER_RADIANCE, fp16=True):
+        """Film::WriteImage: the film's image as an (uncompressed scanline) OpenEXR file, packed on the device."""
+        capi.check(self._L.b200pt_film_write_exr(self._r, int(channels), str(path).encode(), 1 if fp16 else 0), self.agg._ctx)
+
     def film_device_ptr(self):
         p, n = C.c_void_p(), C.c_uint64()
         capi.check(self._L.b200pt_film_device_ptr(self._r, C.byref(p), C.byref(n)), self.agg._ctx)

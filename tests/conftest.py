@@ -110,3 +110,50 @@ def rendercheck(P):
 def rrmse(img, ref):
     """relative RMSE the way SURVEY.md 8c states the image gate: sqrt(mean((a-b)^2)) / mean(ref)."""
     return float(np.sqrt(np.mean((np.asarray(img, np.float64) - ref) ** 2)) / np.mean(ref))
+
+
+def read_exr(path):
+    """Minimal reader of an uncompressed scanline OpenEXR file (what b200pt_film_write_exr writes; the layout is the
+    OpenEXR file-format document's): -> (dict name -> (H, W) float32 array, dataWindow, displayWindow)."""
+    import struct
+    b = open(path, "rb").read()
+    assert struct.unpack_from("<i", b, 0)[0] == 20000630 and struct.unpack_from("<i", b, 4)[0] == 2
+    p, attrs = 8, {}
+    while b[p] != 0:
+        e = b.index(b"\0", p)
+        name = b[p:e].decode()
+        p = e + 1
+        e = b.index(b"\0", p)
+        typ = b[p:e].decode()
+        p = e + 1
+        size = struct.unpack_from("<i", b, p)[0]
+        p += 4
+        attrs[name] = (typ, b[p:p + size])
+        p += size
+    p += 1
+    chans, q, v = [], 0, attrs["channels"][1]
+    while v[q] != 0:
+        e = v.index(b"\0", q)
+        nm = v[q:e].decode()
+        ptype, _, xs, ys = struct.unpack_from("<i4sii", v, e + 1)
+        assert xs == 1 and ys == 1
+        chans.append((nm, ptype))
+        q = e + 1 + 16
+    assert [c[0] for c in chans] == sorted(c[0] for c in chans), "EXR channel lists are sorted by name"
+    assert attrs["compression"][1] == b"\0" and attrs["lineOrder"][1] == b"\0"
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    disp = struct.unpack("<4i", attrs["displayWindow"][1])
+    w, h = x1 - x0 + 1, y1 - y0 + 1
+    offs = np.frombuffer(b, "<u8", h, p)
+    out = {nm: np.empty((h, w), np.float32) for nm, _ in chans}
+    for k in range(h):
+        o = int(offs[k])
+        y, nbytes = struct.unpack_from("<ii", b, o)
+        assert y == y0 + k
+        o += 8
+        for nm, ptype in chans:
+            dt = "<f2" if ptype == 1 else "<f4"
+            out[nm][k] = np.frombuffer(b, dt, w, o).astype(np.float32)
+            o += w * (2 if ptype == 1 else 4)
+        assert o - int(offs[k]) - 8 == nbytes
+    return out, (x0, y0, x1, y1), disp

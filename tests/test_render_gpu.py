@@ -341,3 +341,42 @@ def test_config4_gbuffer_matches_reference(P):
     # ids where a camera ray found a surface in every sample (vignetted / escaped samples leave the reference's
     # VisibleSurface default-constructed: indeterminate ids)
     assert (img[..., 37] == ref[..., 37]).mean() > 0.98 and (img[..., 38] == ref[..., 38]).mean() > 0.98
+
+
+def test_film_write_exr(P, tmp_path):
+    """b200pt_film_write_exr (Film::WriteImage's .exr case, SURVEY 8f N4): the GBufferFilm image packed on the device
+    into an uncompressed scanline EXR under the reference's channel names, float (bit-identical to the image call) and
+    half (clamped, rounded to nearest); an RGB film's three channels likewise."""
+    from conftest import read_exr
+    rsc = P.RenderScene.load(os.path.join(GOLD, "cornell_gbuffer_r48_s16.b2rs"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img = r.gbuffer_image(P.scenes.GBUFFER_ALL)
+        r.write_exr(tmp_path / "f32.exr", P.scenes.GBUFFER_ALL, fp16=False)
+        r.write_exr(tmp_path / "f16.exr", fp16=True)  # the film's default groups: R G B + Radiance
+    finally:
+        r.close()
+    names = (["R", "G", "B"] + [f"Radiance.C{i:02d}" for i in range(1, 32)] + ["P.X", "P.Y", "P.Z", "MaterialId", "InstanceId",
+             "Ns.X", "Ns.Y", "Nx.Z", "N.X", "N.Y", "N.Z", "Variance.R", "Variance.G", "Variance.B",
+             "RelativeVariance.R", "RelativeVariance.G", "RelativeVariance.B"])
+    ch, data, disp = read_exr(tmp_path / "f32.exr")
+    assert sorted(ch) == sorted(names) and data == (0, 0, 47, 47) and disp == (0, 0, 47, 47)
+    for k, nm in enumerate(names):
+        np.testing.assert_array_equal(ch[nm], img[..., k], err_msg=nm)
+    ch16, _, _ = read_exr(tmp_path / "f16.exr")
+    assert sorted(ch16) == sorted(names[:34])
+    for k, nm in enumerate(names[:34]):
+        np.testing.assert_array_equal(ch16[nm], np.minimum(img[..., k], 65504).astype(np.float16).astype(np.float32), err_msg=nm)
+    rsc = P.RenderScene.load(os.path.join(GOLD, "cornell_r64_s16.b2rs"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        rgb = r.image()
+        r.write_exr(tmp_path / "rgb.exr", fp16=False)
+    finally:
+        r.close()
+    ch, _, _ = read_exr(tmp_path / "rgb.exr")
+    assert sorted(ch) == ["B", "G", "R"]
+    for k, nm in enumerate("RGB"):
+        np.testing.assert_array_equal(ch[nm], rgb[..., k])
