@@ -168,10 +168,12 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         }
     }
     r.film_type = T.at("film_type").u()[0];
-    if (r.film_type == 2)
-        die("pbrt_b200: Film \"gbuffer\" writes EXR only (film.cpp:1081-1083) and the oracle build has no EXR writer "
-            "(oracle/ref.mk); the GBufferFilm path is exercised through libb200pt.so directly (tests/test_render_gpu.py)");
-    if (r.film_type == 1) {
+    if (r.film_type == 2) {  // GBufferFilm: the AOVs' output space and the host's material ids
+        memcpy(r.gbuffer_output_from_render, T.at("gbuffer_from_render").f(), 64);
+        memcpy(r.gbuffer_output_from_render_inv, T.at("gbuffer_from_render_inv").f(), 64);
+        r.material_ids = T.at("material_ids").i();
+    }
+    if (r.film_type == 1 || r.film_type == 2) {
         const float *fs = T.at("film_spectral").f();
         r.n_buckets = uint32_t(fs[0]);
         r.lambda_min = fs[1];
@@ -324,6 +326,27 @@ static void RenderB200(BasicScene &scene, int device, bool hostBvh) {
     check(b200pt_context_sync(ctx), ctx, "b200pt_context_sync");
     const double seconds = std::chrono::duration<double>(clk::now() - t0).count();
 
+    if (GBufferFilm *gf = ro.film.CastOrNullptr<GBufferFilm>()) {
+        // GBufferFilm writes EXR only (film.cpp:1081-1083) and the oracle build of the reference has no EXR writer
+        // (oracle/ref.mk): the library's own - image finalised and packed on the device - writes the file, with the
+        // channel groups the film's save* switches ask for.  (Albedo, dzdx / dzdy and the SVD basis are not built.)
+        if (gf->writeAlbedo || gf->writeDz || gf->writeBasis) die("pbrt_b200: saveAlbedo / saveDz / saveRadianceAsBasis are not built");
+        uint32_t ch = (gf->writeRadiance ? B200PT_GBUFFER_RADIANCE : 0) | (gf->writePosition ? B200PT_GBUFFER_POSITION : 0) |
+                      (gf->writeMaterial ? B200PT_GBUFFER_MATERIAL : 0) | (gf->writeInstance ? B200PT_GBUFFER_INSTANCE : 0) |
+                      (gf->writeNs ? B200PT_GBUFFER_NS : 0) | (gf->writeNormal ? B200PT_GBUFFER_NORMAL : 0) |
+                      (gf->writeVariance ? B200PT_GBUFFER_VARIANCE : 0) |
+                      (gf->writeRelativeVariance ? B200PT_GBUFFER_RELATIVE_VARIANCE : 0);
+        check(b200pt_film_write_exr(rd, ch, gf->GetFilename().c_str(), gf->writeFP16 ? 1 : 0), ctx, "b200pt_film_write_exr");
+        b200pt_render_stats st{};
+        b200pt_render_get_stats(rd, &st);
+        fprintf(stderr, "pbrt_b200: %llu samples in %.3f s (gpu %.1f ms, %u launches, %llu + %llu rays) -> %s\n",
+                (unsigned long long)st.samples, seconds, st.gpu_ms, st.kernel_launches, (unsigned long long)st.closest_rays,
+                (unsigned long long)st.shadow_rays, gf->GetFilename().c_str());
+        b200pt_render_destroy(rd);
+        b200pt_scene_destroy(sc);
+        b200pt_context_destroy(ctx);
+        return;
+    }
     // the device film accumulators, back into the reference's Film object (row major over pixelBounds, Array2D order)
     Bounds2i pb = ro.film.PixelBounds();
     const size_t nPix = size_t(pb.Area());

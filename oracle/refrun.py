@@ -119,7 +119,7 @@ def render_b200(pbrt_file, out_pfm, wavefront=False, extra=(), timeout=3600):
     dt = time.time() - t
     if r.returncode != 0:
         raise RuntimeError(f"pbrt_b200 failed ({r.returncode}): {r.stderr[-2000:]}")
-    return read_pfm(out_pfm), dt, r.stderr
+    return (read_pfm(out_pfm) if out_pfm else None), dt, r.stderr
 
 
 def render_wavefront(pbrt_file, out_pfm, nthreads=None, timeout=3600):

@@ -62,3 +62,23 @@ def test_wavefront_over_b200_aggregate(P, dropin, tmp_path, kind):
     assert closest > 0 and mismatches == 0
     assert (shadow > 0) if kind != "volpath" else (single > 0)  # volpath: shadow rays walk through IntersectShadowTr
     assert rrmse(img, ref) <= 1e-5, rrmse(img, ref)
+
+
+def test_render_b200_gbuffer_exr(P, dropin, tmp_path):
+    """A .pbrt with the ISET film (`Film "gbuffer"`, EXR only) through the compiled drop-in: the reference's parser and
+    scene objects, the GPU frame, the file written by b200pt_film_write_exr (device-side packing) - against the
+    reference's own Film::GetImage of the same file (dumpscene_ref --render; the oracle build has no EXR writer)."""
+    from conftest import read_exr
+    pbrt, out = str(tmp_path / "g.pbrt"), str(tmp_path / "g.exr")
+    P.scenes.cornell_pbrt(pbrt, out=out, res=48, spp=16, maxdepth=5, film="gbuffer", smooth="instanced")
+    ref, names, _ = dropin.render_channels(pbrt)
+    _, _, log = dropin.render_b200(pbrt, None)
+    assert "samples in" in log
+    ch, data, _ = read_exr(out)
+    assert data == (0, 0, 47, 47) and set(ch) == set(names)
+    for k, nm in enumerate(names):
+        a, b = ch[nm].astype(np.float64), ref[..., k].astype(np.float64)
+        if nm in ("MaterialId", "InstanceId"):
+            assert np.array_equal(a, b), nm
+        else:
+            assert np.sqrt(np.mean((a - b) ** 2)) <= 1e-3 * max(np.mean(np.abs(b)), 1e-12), nm
