@@ -214,7 +214,9 @@ enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC =
 typedef struct b200pt_material {
     uint32_t type;
     int32_t spectrum[4]; /* diffuse: [0] reflectance (materials.h:430-476) */
-    float params[8];
+    float params[8];     /* dielectric: {uRoughness, vRoughness, remapRoughness, eta is a ConstantSpectrum, THIN};
+                          * THIN != 0 = ThinDielectricMaterial (materials.h:215-262, ThinDielectricBxDF bxdfs.h:342-410):
+                          * specular reflection + straight-through transmission, the roughness entries are ignored */
 } b200pt_material;
 
 /* DiffuseAreaLight on one triangle or one bilinear patch (lights.h:407-500; `tri` is then the patch index of a

@@ -629,6 +629,12 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             prm[1] = constFloat(em->vRoughness);
             prm[2] = em->remapRoughness ? 1.f : 0.f;
             prm[3] = em->eta.Is<ConstantSpectrum>() ? 1.f : 0.f;
+        } else if (const ThinDielectricMaterial *tm = mtl.CastOrNullptr<ThinDielectricMaterial>()) {
+            if (tm->displacement || tm->normalMap) die("displacement / normal maps are not dumped");
+            rec[0] = 2;  // the dielectric queue, params[4] = thin
+            rec[1] = pool.add(tm->eta, 1);
+            prm[3] = tm->eta.Is<ConstantSpectrum>() ? 1.f : 0.f;
+            prm[4] = 1.f;
         } else if (const CoatedDiffuseMaterial *cd = mtl.CastOrNullptr<CoatedDiffuseMaterial>()) {
             if (cd->displacement || cd->normalMap) die("displacement / normal maps are not dumped");
             rec[0] = 3;

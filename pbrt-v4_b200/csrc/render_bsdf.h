@@ -177,6 +177,7 @@ struct Bsdf {
     uint32_t type;      // MaterialType
     TRDist tr;          // conductor, dielectric
     float eta;          // dielectric: eta(lambda[0])
+    uint32_t thin;      // dielectric: ThinDielectricBxDF (bxdfs.h:342-410) instead of DielectricBxDF
     int32_t specA;      // diffuse, coated diffuse: reflectance; conductor: eta, or reflectance when specB < 0
     int32_t specB;      // conductor: k
     // coated diffuse (LayeredBxDF<DielectricBxDF, DiffuseBxDF, true>, bxdfs.h:565-1041)
@@ -293,7 +294,8 @@ B2_HD uint32_t BsdfFlags(const Bsdf &b) {
     switch (b.type) {
     case MAT_DIFFUSE: return BX_REFLECTION | BX_DIFFUSE;  // R is never all-zero-checked here; see ShadeVertex
     case MAT_CONDUCTOR: return BX_REFLECTION | (TRSmooth(b.tr) ? BX_SPECULAR : BX_GLOSSY);
-    case MAT_DIELECTRIC: {  // bxdfs.h:300-306
+    case MAT_DIELECTRIC: {  // bxdfs.h:300-306; thin: bxdfs.h:404-406
+        if (b.thin) return BX_REFLECTION | BX_TRANSMISSION | BX_SPECULAR;
         uint32_t f = (b.eta == 1) ? BX_TRANSMISSION : (BX_REFLECTION | BX_TRANSMISSION);
         return f | (TRSmooth(b.tr) ? BX_SPECULAR : BX_GLOSSY);
     }
@@ -309,6 +311,7 @@ B2_HD uint32_t BsdfFlags(const Bsdf &b) {
     return 0;
 }
 B2_HD void BsdfRegularize(Bsdf &b) {
+    if (b.type == MAT_DIELECTRIC && b.thin) return;  // ThinDielectricBxDF::Regularize does nothing (bxdfs.h:400-401)
     if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC || b.type == MAT_COATED_DIFFUSE) TRRegularize(b.tr);
 }
 
@@ -416,6 +419,29 @@ B2_HD BsdfSample BsdfSampleF(const Bsdf &b, V3 wo, float uc, float u0, float u1,
         s.pdf = pdf;
         s.flags = BX_GLOSSY | BX_REFLECTION;
         s.ok = true;
+        return s;
+    }
+    if (b.type == MAT_DIELECTRIC && b.thin) {  // ThinDielectricBxDF::Sample_f (bxdfs.h:355-386)
+        ev.kind = 1;
+        float Rf = FrDielectric(AbsCosTheta(wo), b.eta), T = 1 - Rf;
+        if (Rf < 1) {  // scattering between the two interfaces
+            Rf += SqrF(T) * Rf / (1 - SqrF(Rf));
+            T = 1 - Rf;
+        }
+        const float pr = Rf, pt = T;
+        if (pr == 0 && pt == 0) return s;
+        s.ok = true;
+        if (uc < pr / (pr + pt)) {
+            s.wi = mk(-wo.x, -wo.y, wo.z);
+            ev.scale = Rf / AbsCosTheta(s.wi);
+            s.pdf = pr / (pr + pt);
+            s.flags = BX_SPECULAR | BX_REFLECTION;
+        } else {
+            s.wi = -wo;
+            ev.scale = T / AbsCosTheta(s.wi);
+            s.pdf = pt / (pr + pt);
+            s.flags = BX_SPECULAR | BX_TRANSMISSION;
+        }
         return s;
     }
     if (b.type == MAT_DIELECTRIC) {  // bxdfs.cpp:77-165

@@ -119,6 +119,7 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
     b.type = MAT >= 0 ? uint32_t(MAT) : mat.type;
     b.tr = TRDist{0, 0};
     b.eta = 1;
+    b.thin = 0;
     b.specA = mat.spectrum[0];
     b.specB = -1;
     b.thickness = 0;
@@ -147,6 +148,10 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
         if (mat.params[3] == 0) p.flags |= PF_TERMINATED_SECONDARY;  // eta is not a ConstantSpectrum
         if (e == 0) e = 1;
         b.eta = e;
+        if (mat.params[4] != 0) {  // ThinDielectricMaterial (materials.h:215-262): no roughness
+            b.thin = 1;
+            b.tr = TRDist{0, 0};
+        }
     }
     if (b.type == MAT_COATED_DIFFUSE) {  // CoatedDiffuseMaterial::GetBxDF (materials.cpp:301-329)
         float e = SpectrumAt(rs.spectra[mat.spectrum[2]], lambda0);

@@ -352,6 +352,8 @@ MATERIALS = {
     "dielectric_smooth": 'Material "dielectric" "float eta" 1.5',
     "dielectric_rough": 'Material "dielectric" "float eta" 1.5 "float roughness" 0.1',
     "dielectric_glass": 'Material "dielectric" "spectrum eta" "glass-BK7"',
+    "thin_dielectric": 'Material "thindielectric" "float eta" 1.5',
+    "thin_dielectric_glass": 'Material "thindielectric" "spectrum eta" "glass-BK7"',
     "coated_diffuse": 'Material "coateddiffuse" "rgb reflectance" [0.2 0.3 0.7] "float roughness" 0',
     "coated_diffuse_rough": 'Material "coateddiffuse" "rgb reflectance" [0.7 0.3 0.2] "float roughness" 0.1 "float thickness" 0.02',
 }

@@ -201,6 +201,8 @@ TIGHT_CASES = {
                                      regularize=True)),
     "tight_coated": ("cornell", dict(res=32, spp=1024, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough"))),
     "tight_alpha": ("cornell", dict(res=32, spp=1024, maxdepth=5, alpha=True)),
+    # ThinDielectricMaterial: a constant-eta pane and one with a dispersive index (TerminateSecondary)
+    "tight_thin": ("cornell", dict(res=32, spp=16384, maxdepth=6, boxes=("thin_dielectric", "thin_dielectric_glass"))),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),
 }
