@@ -213,7 +213,9 @@ typedef struct b200pt_spectrum {
 enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2, B200PT_MAT_COATED_DIFFUSE = 3 };
 typedef struct b200pt_material {
     uint32_t type;
-    int32_t spectrum[4]; /* diffuse: [0] reflectance (materials.h:430-476) */
+    int32_t spectrum[4]; /* diffuse: [0] reflectance (materials.h:430-476); with params[4] != 0 the material is a
+                          * DiffuseTransmissionMaterial (materials.h:869-927, DiffuseTransmissionBxDF bxdfs.h:218-297):
+                          * [0] reflectance, [1] transmittance, params[5] = scale */
     float params[8];     /* dielectric: {uRoughness, vRoughness, remapRoughness, eta is a ConstantSpectrum, THIN};
                           * THIN != 0 = ThinDielectricMaterial (materials.h:215-262, ThinDielectricBxDF bxdfs.h:342-410):
                           * specular reflection + straight-through transmission, the roughness entries are ignored */

@@ -612,6 +612,13 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             if (dm->displacement || dm->normalMap) die("displacement / normal maps are not dumped");
             rec[0] = 0;
             rec[1] = constSpec(dm->reflectance);
+        } else if (const DiffuseTransmissionMaterial *dt = mtl.CastOrNullptr<DiffuseTransmissionMaterial>()) {
+            if (dt->displacement || dt->normalMap) die("displacement / normal maps are not dumped");
+            rec[0] = 0;  // the diffuse queue, params[4] = transmission
+            rec[1] = constSpec(dt->reflectance);
+            rec[2] = constSpec(dt->transmittance);
+            prm[4] = 1.f;
+            prm[5] = dt->scale;
         } else if (const ConductorMaterial *cm = mtl.CastOrNullptr<ConductorMaterial>()) {
             if (cm->displacement || cm->normalMap) die("displacement / normal maps are not dumped");
             rec[0] = 1;
@@ -650,7 +657,7 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             prm[6] = float(cd->maxDepth);
             prm[7] = float(cd->nSamples);
         } else
-            die("only diffuse, conductor, dielectric and coateddiffuse materials are dumped so far");
+            die("only diffuse, diffusetransmission, conductor, dielectric, thindielectric and coateddiffuse materials are dumped so far");
         matI.insert(matI.end(), rec, rec + 5);
         matF.insert(matF.end(), prm, prm + 8);
     }

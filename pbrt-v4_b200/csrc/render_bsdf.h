@@ -163,6 +163,7 @@ struct BsdfSample {
 // 3 conductor ((D*F_k)*G)/denom with F_k = FrComplex(cosF, eta_k, k_k), 4 specular conductor F_k/denom.
 // 5 coated diffuse: sum_a poly[a] * R_k^a (the random walk of LayeredBxDF only ever multiplies the
 // throughput by scalars and by the diffuse base's R_k, so its value is a polynomial in R_k).
+// 6 / 7 diffuse transmission: clamp(dscale*R_k)*scale on wo's side, clamp(dscale*T_k)*scale on the other.
 constexpr int kLayerPoly = 14;
 struct BsdfEval {
     int kind;
@@ -178,6 +179,8 @@ struct Bsdf {
     TRDist tr;          // conductor, dielectric
     float eta;          // dielectric: eta(lambda[0])
     uint32_t thin;      // dielectric: ThinDielectricBxDF (bxdfs.h:342-410) instead of DielectricBxDF
+    uint32_t trans;     // diffuse: DiffuseTransmissionBxDF (bxdfs.h:218-297): specA = reflectance, specB = transmittance,
+    float dscale, tMax; //   both times dscale and clamped to [0, 1]; rMax / tMax = their maxima at the path's wavelengths
     int32_t specA;      // diffuse, coated diffuse: reflectance; conductor: eta, or reflectance when specB < 0
     int32_t specB;      // conductor: k
     // coated diffuse (LayeredBxDF<DielectricBxDF, DiffuseBxDF, true>, bxdfs.h:565-1041)
@@ -292,7 +295,10 @@ B2_HD_CALL BsdfSample DielSample(float eta, TRDist tr, V3 wo, float uc, float u0
 
 B2_HD uint32_t BsdfFlags(const Bsdf &b) {
     switch (b.type) {
-    case MAT_DIFFUSE: return BX_REFLECTION | BX_DIFFUSE;  // R is never all-zero-checked here; see ShadeVertex
+    case MAT_DIFFUSE:
+        if (b.trans)  // bxdfs.h:288-291
+            return (b.rMax != 0 ? (BX_REFLECTION | BX_DIFFUSE) : 0u) | (b.tMax != 0 ? (BX_TRANSMISSION | BX_DIFFUSE) : 0u);
+        return BX_REFLECTION | BX_DIFFUSE;  // R is never all-zero-checked here; see ShadeVertex
     case MAT_CONDUCTOR: return BX_REFLECTION | (TRSmooth(b.tr) ? BX_SPECULAR : BX_GLOSSY);
     case MAT_DIELECTRIC: {  // bxdfs.h:300-306; thin: bxdfs.h:404-406
         if (b.thin) return BX_REFLECTION | BX_TRANSMISSION | BX_SPECULAR;
@@ -327,6 +333,11 @@ B2_HD BsdfEval ZeroEval() {
 B2_HD BsdfEval BsdfF(const Bsdf &b, V3 wo, V3 wi) {
     BsdfEval e = ZeroEval();
     if (b.type == MAT_DIFFUSE) {  // DiffuseBxDF::f (bxdfs.h:37-42)
+        if (b.trans) {  // DiffuseTransmissionBxDF::f (bxdfs.h:226-228)
+            e.kind = SameHemisphere(wo, wi) ? 6 : 7;
+            e.scale = kInvPi;
+            return e;
+        }
         if (!SameHemisphere(wo, wi)) return e;
         e.kind = 2;
         e.scale = kInvPi;
@@ -361,6 +372,11 @@ B2_HD BsdfEval BsdfF(const Bsdf &b, V3 wo, V3 wi) {
 // BxDF::PDF(wo, wi, Radiance, All)
 B2_HD float BsdfPDF(const Bsdf &b, V3 wo, V3 wi) {
     if (b.type == MAT_DIFFUSE) {  // bxdfs.h:60-67
+        if (b.trans) {  // DiffuseTransmissionBxDF::PDF (bxdfs.h:263-278)
+            float pr = b.rMax, pt = b.tMax;
+            if (pr == 0 && pt == 0) return 0;
+            return (SameHemisphere(wo, wi) ? pr : pt) / (pr + pt) * (AbsCosTheta(wi) * kInvPi);
+        }
         if (!SameHemisphere(wo, wi)) return 0;
         return AbsCosTheta(wi) * kInvPi;
     }
@@ -380,6 +396,20 @@ B2_HD float BsdfPDF(const Bsdf &b, V3 wo, V3 wi) {
 B2_HD BsdfSample BsdfSampleF(const Bsdf &b, V3 wo, float uc, float u0, float u1, BsdfEval &ev) {
     BsdfSample s{false, mk(0, 0, 0), 0, 0, 1, false};
     ev = ZeroEval();
+    if (b.type == MAT_DIFFUSE && b.trans) {  // DiffuseTransmissionBxDF::Sample_f (bxdfs.h:230-261)
+        float pr = b.rMax, pt = b.tMax;
+        if (pr == 0 && pt == 0) return s;
+        bool reflect = uc < pr / (pr + pt);
+        V3 wi = SampleCosineHemisphere(u0, u1);
+        if (reflect ? wo.z < 0 : wo.z > 0) wi.z *= -1;
+        s.wi = wi;
+        s.pdf = AbsCosTheta(wi) * kInvPi * (reflect ? pr : pt) / (pr + pt);
+        s.flags = BX_DIFFUSE | (reflect ? BX_REFLECTION : BX_TRANSMISSION);
+        ev.kind = reflect ? 6 : 7;
+        ev.scale = kInvPi;
+        s.ok = true;
+        return s;
+    }
     if (b.type == MAT_DIFFUSE) {  // bxdfs.h:44-58
         V3 wi = SampleCosineHemisphere(u0, u1);
         if (wo.z < 0) wi.z *= -1;

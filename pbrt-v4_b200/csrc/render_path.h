@@ -120,6 +120,9 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
     b.tr = TRDist{0, 0};
     b.eta = 1;
     b.thin = 0;
+    b.trans = 0;
+    b.dscale = 1;
+    b.tMax = 0;
     b.specA = mat.spectrum[0];
     b.specB = -1;
     b.thickness = 0;
@@ -152,6 +155,20 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
             b.thin = 1;
             b.tr = TRDist{0, 0};
         }
+    }
+    if (b.type == MAT_DIFFUSE && mat.params[4] != 0) {  // DiffuseTransmissionMaterial::GetBxDF (materials.h:891-897)
+        b.trans = 1;
+        b.specB = mat.spectrum[1];
+        b.dscale = mat.params[5];
+        float rm = 0, tm = 0;
+        LambdaIter li(p.lambdaU);
+B2_SPECTRAL_LOOP
+        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+            rm = fmaxf(rm, Clampf(b.dscale * SpectrumAt(rs.spectra[b.specA], li.lam), 0, 1));
+            tm = fmaxf(tm, Clampf(b.dscale * SpectrumAt(rs.spectra[b.specB], li.lam), 0, 1));
+        }
+        b.rMax = rm;
+        b.tMax = tm;
     }
     if (b.type == MAT_COATED_DIFFUSE) {  // CoatedDiffuseMaterial::GetBxDF (materials.cpp:301-329)
         float e = SpectrumAt(rs.spectra[mat.spectrum[2]], lambda0);
@@ -187,6 +204,8 @@ B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval
     switch (e.kind) {
     case 1: return e.scale;
     case 2: return Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, 1) * e.scale;  // DiffuseMaterial clamps R
+    case 6: return Clampf(b.dscale * SpectrumAt(rs.spectra[b.specA], lam), 0, 1) * e.scale;  // DiffuseTransmission: R
+    case 7: return Clampf(b.dscale * SpectrumAt(rs.spectra[b.specB], lam), 0, 1) * e.scale;  //   T (materials.h:894-895)
     case 5: {  // coated diffuse: polynomial in R_k (render_layered.h)
         float R = Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, 1);
         float v = e.poly[kLayerPoly - 1];
@@ -387,7 +406,7 @@ B2_SPECTRAL_LOOP
         io.VisibleSurface(Mid(si.pi), DotN(si.n, si.wo) < 0 ? -si.n : si.n, DotN(si.ns, si.wo) < 0 ? -si.ns : si.ns,
                           mesh.material, (int)hit[5]);
     uint32_t bflags = BsdfFlags(bsdf);
-    if (bsdf.type == MAT_DIFFUSE) {  // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
+    if (bsdf.type == MAT_DIFFUSE && !bsdf.trans) {  // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
         bool anyR = false;
         LambdaIter li(p.lambdaU);
 B2_SPECTRAL_LOOP

@@ -354,6 +354,8 @@ MATERIALS = {
     "dielectric_glass": 'Material "dielectric" "spectrum eta" "glass-BK7"',
     "thin_dielectric": 'Material "thindielectric" "float eta" 1.5',
     "thin_dielectric_glass": 'Material "thindielectric" "spectrum eta" "glass-BK7"',
+    "diffuse_transmission": 'Material "diffusetransmission" "rgb reflectance" [0.3 0.5 0.2] "rgb transmittance" [0.5 0.4 0.2]',
+    "diffuse_transmission_scaled": 'Material "diffusetransmission" "rgb reflectance" [0.1 0.1 0.1] "rgb transmittance" [0.3 0.45 0.6] "float scale" 1.8',
     "coated_diffuse": 'Material "coateddiffuse" "rgb reflectance" [0.2 0.3 0.7] "float roughness" 0',
     "coated_diffuse_rough": 'Material "coateddiffuse" "rgb reflectance" [0.7 0.3 0.2] "float roughness" 0.1 "float thickness" 0.02',
 }

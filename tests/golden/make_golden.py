@@ -203,6 +203,9 @@ TIGHT_CASES = {
     "tight_alpha": ("cornell", dict(res=32, spp=1024, maxdepth=5, alpha=True)),
     # ThinDielectricMaterial: a constant-eta pane and one with a dispersive index (TerminateSecondary)
     "tight_thin": ("cornell", dict(res=32, spp=16384, maxdepth=6, boxes=("thin_dielectric", "thin_dielectric_glass"))),
+    # DiffuseTransmissionMaterial: one with the default scale, one whose scale pushes T into the clamp
+    "tight_dtrans": ("cornell", dict(res=32, spp=4096, maxdepth=5,
+                                     boxes=("diffuse_transmission", "diffuse_transmission_scaled"))),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),
 }
@@ -211,7 +214,10 @@ TIGHT_CASES = {
 def make_tight_goldens(P, refrun, out):
     import tempfile
     gen = {"cornell": P.scenes.cornell_pbrt, "config3": P.scenes.config3_pbrt, "config5": P.scenes.config5_pbrt}
+    pick = os.environ.get("B200PT_TIGHT_CASES")  # comma-separated names: regenerate those only
     for name, (kind, kw) in TIGHT_CASES.items():
+        if pick and name not in pick.split(","):
+            continue
         with tempfile.TemporaryDirectory() as tmp:
             pbrt, pfm = os.path.join(tmp, name + ".pbrt"), os.path.join(tmp, name + ".pfm")
             imgs = []
