@@ -225,7 +225,11 @@ typedef struct b200pt_material {
  * B200PT_MESH_BILINEAR mesh, sampled as BilinearPatch::Sample, shapes.cpp:1158-1372) or a UniformInfiniteLight (lights.h:512-554:
  * spectrum + scale only; mesh/tri unused) + its PowerLightSampler alias-table bin
  * (lightsamplers.cpp:76-96, util/sampling.cpp:562-617).  Order = the host's `lights` vector. */
-enum { B200PT_LIGHT_AREA_TRIANGLE = 0, B200PT_LIGHT_UNIFORM_INFINITE = 1 };
+/* B200PT_LIGHT_POINT / SPOT / DISTANT: PointLight (lights.h:189-239), SpotLight (lights.h:747-801), DistantLight
+ * (lights.h:242-297) - `spectrum` is I / Lemit, `scale` the light's scale; mesh / tri and the falloff fields are
+ * unused, the placement comes from b200pt_render_desc::light_geometry. */
+enum { B200PT_LIGHT_AREA_TRIANGLE = 0, B200PT_LIGHT_UNIFORM_INFINITE = 1, B200PT_LIGHT_POINT = 2, B200PT_LIGHT_SPOT = 3,
+       B200PT_LIGHT_DISTANT = 4 };
 typedef struct b200pt_light {
     uint32_t mesh, tri;
     int32_t spectrum; /* Lemit */
@@ -371,7 +375,14 @@ typedef struct b200pt_render_desc {
      * uniform sample offsets, weight 1) is implemented; any other value is refused with B200PT_ERR_INVALID - pbrt's
      * default is the Gaussian, a host adaptor must say so instead of getting a box-filtered image silently. */
     uint32_t filter_type;
+    /* placement of the delta lights, B200PT_LIGHT_GEOMETRY_FLOATS floats per light for ALL n_lights lights (rows of
+     * other light types are ignored); NULL when the scene has none.  Row: [0..2] point / spot: renderFromLight(0,0,0)
+     * (lights.h:224, 787); distant: Normalize(renderFromLight(0,0,1)) (lights.h:285); [3] distant: sceneRadius
+     * (DistantLight::Preprocess, lights.h:277-279); [4..12] spot: upper 3 x 3 of renderFromLight's inverse, row major
+     * (lights.h:790); [13] spot cosFalloffStart, [14] spot cosFalloffEnd (lights.cpp:1376-1385); [15] 0. */
+    const float *light_geometry;
 } b200pt_render_desc;
+#define B200PT_LIGHT_GEOMETRY_FLOATS 16
 enum { B200PT_FILTER_BOX = 0, B200PT_FILTER_GAUSSIAN = 1, B200PT_FILTER_MITCHELL = 2, B200PT_FILTER_SINC = 3, B200PT_FILTER_TRIANGLE = 4 };
 
 typedef struct b200pt_render b200pt_render;

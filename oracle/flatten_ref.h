@@ -672,7 +672,7 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
     // ---- lights + the power sampler's alias table (lightsamplers.cpp:76-96, util/sampling.cpp:562-617)
     PowerLightSampler pls(pstd::span<const Light>(lights.data(), lights.size()), Allocator());
     std::vector<int32_t> lightI;
-    std::vector<float> lightF;
+    std::vector<float> lightF, lightGeom;
     std::map<const void *, int> lemitId;
     for (size_t i = 0; i < lights.size(); ++i) {
         const auto &bin = pls.aliasTable.bins[i];
@@ -682,8 +682,36 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             lightF.insert(lightF.end(), {ul->scale, 0.f, 0.f, 0.f, bin.q, bin.p});
             continue;
         }
+        // the delta lights: placement in lights_geom (include/b200pt.h b200pt_render_desc::light_geometry)
+        auto deltaLight = [&](int type, const DenselySampledSpectrum *spec, float scale, const float (&g)[16]) {
+            if (!lemitId.count(spec)) lemitId[spec] = pool.add(spec, 0);
+            lightI.insert(lightI.end(), {-1, -1, lemitId[spec], 0, bin.alias, -1, type});
+            lightF.insert(lightF.end(), {scale, 0.f, 0.f, 0.f, bin.q, bin.p});
+            if (lightGeom.empty()) lightGeom.assign(16 * lights.size(), 0.f);
+            std::copy(g, g + 16, lightGeom.begin() + 16 * i);
+        };
+        if (const PointLight *pl = lights[i].CastOrNullptr<PointLight>()) {
+            Point3f p = pl->renderFromLight(Point3f(0, 0, 0));
+            float g[16] = {p.x, p.y, p.z};
+            deltaLight(2, pl->I, pl->scale, g);
+            continue;
+        }
+        if (const SpotLight *sl = lights[i].CastOrNullptr<SpotLight>()) {
+            Point3f p = sl->renderFromLight(Point3f(0, 0, 0));
+            const SquareMatrix<4> &mi = sl->renderFromLight.GetInverseMatrix();
+            float g[16] = {p.x, p.y, p.z, 0.f, mi[0][0], mi[0][1], mi[0][2], mi[1][0], mi[1][1], mi[1][2],
+                           mi[2][0], mi[2][1], mi[2][2], sl->cosFalloffStart, sl->cosFalloffEnd, 0.f};
+            deltaLight(3, sl->Iemit, sl->scale, g);
+            continue;
+        }
+        if (const DistantLight *dl = lights[i].CastOrNullptr<DistantLight>()) {
+            Vector3f wi = Normalize(dl->renderFromLight(Vector3f(0, 0, 1)));
+            float g[16] = {wi.x, wi.y, wi.z, dl->sceneRadius};
+            deltaLight(4, dl->Lemit, dl->scale, g);
+            continue;
+        }
         const DiffuseAreaLight *al = lights[i].CastOrNullptr<DiffuseAreaLight>();
-        if (!al) die("only diffuse area lights and uniform infinite lights are dumped so far");
+        if (!al) die("only diffuse area, uniform infinite, point, spot and distant lights are dumped so far");
         if (al->image) die("image area lights are not dumped");
         if (!lemitId.count(al->Lemit)) lemitId[al->Lemit] = pool.add(al->Lemit, 0);
         int m = lightMeshTri[2 * i], tri = lightMeshTri[2 * i + 1];
@@ -693,6 +721,7 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
     }
     w.i32("lights_i", {uint32_t(lights.size()), 7}, lightI);
     w.f32("lights_f", {uint32_t(lights.size()), 6}, lightF);
+    if (!lightGeom.empty()) w.f32("lights_geom", {uint32_t(lights.size()), 16}, lightGeom);
 
     // ---- the light BVH (lightsamplers.cpp:109-232), node fields as include/b200pt.h lists them
     if (lsId == 2) {

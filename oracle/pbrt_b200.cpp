@@ -233,6 +233,7 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         L.alias = a[4];
         L.type = uint32_t(a[6]);
     }
+    if (T.has("lights_geom")) r.light_geometry = T.at("lights_geom").f();
     const Table &ma = T.at("mesh_attr");
     const size_t nMesh = ma.rows();
     m.attrs.resize(std::max<size_t>(1, nMesh));

@@ -260,14 +260,22 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     out.lights.resize(d->n_lights);
     for (uint32_t i = 0; i < d->n_lights; ++i) {
         const b200pt_light &l = d->lights[i];
-        if (l.type > B200PT_LIGHT_UNIFORM_INFINITE) return bad("unsupported light type");
+        if (l.type > B200PT_LIGHT_DISTANT) return bad("unsupported light type");
+        if (l.type >= B200PT_LIGHT_POINT) {
+            if (!d->light_geometry) return bad("point / spot / distant lights need light_geometry");
+            if (out.lightGeom.empty()) out.lightGeom.assign(size_t(kLightGeomFloats) * d->n_lights, 0.f);
+            const float *g = d->light_geometry + size_t(B200PT_LIGHT_GEOMETRY_FLOATS) * i;
+            for (int k = 0; k < kLightGeomFloats; ++k)
+                if (!std::isfinite(g[k])) return bad("light_geometry holds a non-finite value");
+            std::copy(g, g + kLightGeomFloats, out.lightGeom.begin() + size_t(kLightGeomFloats) * i);
+        }
         uint32_t slot = 0;
         if (l.type == B200PT_LIGHT_AREA_TRIANGLE) {
             auto it = slotOf.find((uint64_t(l.mesh) << 32) | l.tri);
             if (it == slotOf.end()) return bad("light refers to a triangle that is not in the scene");
             slot = it->second;
-        } else
-            out.infiniteLights.push_back(int32_t(i));
+        } else if (l.type == B200PT_LIGHT_UNIFORM_INFINITE || l.type == B200PT_LIGHT_DISTANT)
+            out.infiniteLights.push_back(int32_t(i));  // Light::Bounds() is empty (lightsamplers.cpp:114-123)
         if (!specOk(l.spectrum)) return bad("light spectrum index out of range");
         if (l.alias >= int32_t(d->n_lights)) return bad("alias index out of range");
         LightDev &o = out.lights[i];

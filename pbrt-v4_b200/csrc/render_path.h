@@ -260,6 +260,7 @@ B2_HD void EscapedRadianceVol(const RenderSceneDev &rs, float lambdaU, IO &io) {
     const float avg = AvgRu(io);
     for (uint32_t i = 0; i < rs.nInfiniteLights; ++i) {
         const LightDev &light = rs.lights[rs.infiniteLights[i]];
+        if (light.type != LIGHT_UNIFORM_INFINITE) continue;  // a DistantLight: in the sampler's list, LightType::DeltaDirection
         const SpectrumTable &sp = rs.spectra[light.spectrum];
         LambdaIter li(lambdaU);
 B2_SPECTRAL_LOOP
@@ -277,6 +278,7 @@ template <class IO>
 B2_HD void EscapedRadiance(const RenderSceneDev &rs, float lambdaU, bool unweighted, float pB, IO &io) {
     for (uint32_t i = 0; i < rs.nInfiniteLights; ++i) {
         const LightDev &light = rs.lights[rs.infiniteLights[i]];
+        if (light.type != LIGHT_UNIFORM_INFINITE) continue;
         const SpectrumTable &sp = rs.spectra[light.spectrum];
         float w = unweighted ? 1.f : PowerHeuristic(pB, 0.f);
         LambdaIter li(lambdaU);
@@ -467,11 +469,16 @@ B2_SPECTRAL_LOOP
                 ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, uLight0, uLight1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri, lt.kind).n);
             }
             V3 cp = Mid(ctx.pi);
+            // the delta lights (point, spot, distant): pdf 1, no MIS (cpu/integrators.cpp:798-799, 1386-1387)
+            const bool delta = lidx >= 0 && light.type >= LIGHT_POINT;
+            V3 wiDelta = mk(0, 0, 0);
+            float attenDelta = 1.f;
+            if (delta) SampleDeltaLight(light, rs.lightGeom + size_t(kLightGeomFloats) * lidx, cp, ss, wiDelta, attenDelta);
             if (ss.ok && ss.pdf != 0 && LengthSquared(Mid(ss.pi) - cp) != 0) {
-                V3 wi = Normalize(Mid(ss.pi) - cp);
-                if (AreaLightEmits(light, ss.n, -wi)) {
-                    float atten = 1.f;
-                    if (light.cosFalloffEnd > 0) {  // ISET spread angle (lights.cpp:762-770)
+                V3 wi = delta ? wiDelta : Normalize(Mid(ss.pi) - cp);
+                if (delta || AreaLightEmits(light, ss.n, -wi)) {
+                    float atten = attenDelta;
+                    if (!delta && light.cosFalloffEnd > 0) {  // ISET spread angle (lights.cpp:762-770)
                         float cos_a = -DotN(ss.n, wi);
                         float sin_a = SafeSqrt(1 - SqrF(cos_a));
                         float tan_a = sin_a / cos_a;
@@ -482,7 +489,8 @@ B2_SPECTRAL_LOOP
                     if (ev.kind != 0) {
                         float absCos = AbsDotN(si.ns, wi);
                         float p_l = pmf * ss.pdf;
-                        float p_b = woLd.z == 0 ? 0.f : EvalPDF(bsdf, woLd, wiL);
+                        // a delta light: w_l = PowerHeuristic(p_l, 0) = 1 and the volpath estimate divides by r_l alone
+                        float p_b = (woLd.z == 0 || delta) ? 0.f : EvalPDF(bsdf, woLd, wiL);
                         float w_l = PowerHeuristic(p_l, p_b);
                         const SpectrumTable &sp = rs.spectra[light.spectrum];
                         bool anyL = false, anyF = false;

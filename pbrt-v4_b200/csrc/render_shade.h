@@ -239,6 +239,44 @@ struct ShapeSampleOut {
     bool ok;
 };
 
+// Light::SampleLi of the delta lights: PointLight (lights.h:221-228), SpotLight (lights.h:784-795, I(): lights.cpp:1391-1394),
+// DistantLight (lights.h:282-289).  ss.pi = pLight (no error interval, no normal), ss.pdf = 1; *atten = what multiplies
+// scale * spectrum(lambda).  false: the sample carries nothing.
+B2_HD bool SampleDeltaLight(const LightDev &light, const float *g, V3 cp, ShapeSampleOut &ss, V3 &wi, float &atten) {
+    ss.n = mk(0, 0, 0);
+    ss.pdf = 1;
+    if (light.type == LIGHT_DISTANT) {
+        wi = mk(g[0], g[1], g[2]);
+        ss.pi = MakeP3i(cp + wi * (2 * g[3]), mk(0, 0, 0));
+        atten = 1;
+        ss.ok = true;
+        return true;
+    }
+    V3 pl = mk(g[0], g[1], g[2]);
+    wi = Normalize(pl - cp);
+    ss.pi = MakeP3i(pl, mk(0, 0, 0));
+    atten = 1 / LengthSquared(pl - cp);
+    if (light.type == LIGHT_SPOT) {
+        V3 w = -wi;  // wLight = Normalize(renderFromLight.ApplyInverse(-wi))
+        V3 wl = Normalize(mk(g[4] * w.x + g[5] * w.y + g[6] * w.z, g[7] * w.x + g[8] * w.y + g[9] * w.z,
+                             g[10] * w.x + g[11] * w.y + g[12] * w.z));
+        float a = g[14], b = g[13], x = wl.z, sm;  // SmoothStep(CosTheta(w), cosFalloffEnd, cosFalloffStart) (util/math.h)
+        if (a == b)
+            sm = x < a ? 0.f : 1.f;
+        else {
+            float t = Clampf((x - a) / (b - a), 0, 1);
+            sm = t * t * (3 - 2 * t);
+        }
+        atten = sm * atten;  // (smoothstep * scale * I) / d^2
+        if (sm == 0) {
+            ss.ok = false;
+            return false;
+        }
+    }
+    ss.ok = true;
+    return true;
+}
+
 B2_HD float TriArea(const TriVerts &t) { return 0.5f * Length(Cross(t.p1 - t.p0, t.p2 - t.p0)); }  // shapes.h:866-871
 
 // Triangle::Sample(u) by area (shapes.h:1012-1047)

@@ -33,7 +33,8 @@ struct MaterialDev {
 
 // DiffuseAreaLight on one triangle (lights.h:410-470) + its alias-table bin (util/sampling.h:804).
 struct LightDev {
-    uint32_t type;       // 0 = diffuse area light on a triangle, 1 = uniform infinite light
+    uint32_t type;       // 0 = diffuse area light on a triangle, 1 = uniform infinite light; 2 point, 3 spot, 4 distant:
+                         //   the delta lights, whose placement is in RenderSceneDev::lightGeom (kLightGeomFloats per light)
     uint32_t slot;       // PrimSlot of its triangle
     int32_t spectrum;    // Lemit
     float scale;
@@ -43,6 +44,12 @@ struct LightDev {
     int32_t alias;
     uint32_t flipNormal; // mesh reverseOrientation ^ transformSwapsHandedness
 };
+
+enum : uint32_t { LIGHT_AREA = 0, LIGHT_UNIFORM_INFINITE = 1, LIGHT_POINT = 2, LIGHT_SPOT = 3, LIGHT_DISTANT = 4 };
+// lightGeom record of light i: [0..2] point / spot: renderFromLight(0,0,0); distant: Normalize(renderFromLight(0,0,1));
+// [3] distant: sceneRadius (DistantLight::Preprocess, lights.h:277-279); [4..12] spot: the upper 3 x 3 of
+// renderFromLight's inverse, row-major; [13] cosFalloffStart, [14] cosFalloffEnd (lights.cpp:1376-1385); [15] 0
+constexpr int kLightGeomFloats = 16;
 
 struct MeshAttrDev {
     int32_t material;
@@ -142,6 +149,7 @@ struct RenderSceneDev {
     uint32_t nMedia;
     uint32_t geomExt;         // some mesh is a bilinear patch mesh or has per-corner attributes (else the EXT = 0 kernels run)
     const float *cornerAttr;  // per-corner normals / uv of the meshes that have them (MeshAttrDev::nOff, uvOff)
+    const float *lightGeom;   // delta lights' placement (kLightGeomFloats per light, all lights), or null when there are none
     const int32_t *materialIds;  // GBufferFilm: the host's Material::materialId per material (materials.cpp:738), or null
 };
 

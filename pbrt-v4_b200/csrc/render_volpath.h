@@ -39,7 +39,7 @@ B2_HD int MediumAfter(const MeshAttrDev &mesh, V3 n, V3 w, int rayMedium) {
 
 // LightSampler::Sample + Light::SampleLi for a reference point (the light half of SampleLd, cpu/integrators.cpp:1290-1303)
 struct LightPick {
-    bool ok;
+    bool ok, delta;  // delta: pdf 1 and no MIS against phase-function sampling (cpu/integrators.cpp:1386-1387)
     int lidx;
     float pmf, atten;
     ShapeSampleOut ss;
@@ -50,6 +50,7 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
     const bool lightBvh = LBVH < 0 ? rs.integrator.lightSampler == 2 : LBVH == 1;
     LightPick lp;
     lp.ok = false;
+    lp.delta = false;
     lp.atten = 1.f;
     if (rs.nLights == 0) return lp;
     int nl = (int)rs.nLights;
@@ -66,6 +67,11 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
     }
     if (lp.lidx < 0) return lp;
     const LightDev &light = rs.lights[lp.lidx];
+    if (light.type >= LIGHT_POINT) {  // point, spot, distant
+        lp.delta = true;
+        lp.ok = SampleDeltaLight(light, rs.lightGeom + size_t(kLightGeomFloats) * lp.lidx, Mid(ctx.pi), lp.ss, lp.wi, lp.atten);
+        return lp;
+    }
     if (light.type != 0) return lp;  // infinite lights give nothing under allowIncompletePDF
     TriVerts lt = LoadTri(rs.prims, light.slot);
     lp.ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, u0, u1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri, lt.kind).n);
@@ -221,7 +227,7 @@ B2_SPECTRAL_LOOP
             }
             ShadowVolInfo info;
             info.p_l = lp.pmf * lp.ss.pdf;
-            info.scatterPDF = fHat;
+            info.scatterPDF = lp.delta ? 0.f : fHat;
             info.medium = p.medium;
             info.lightPi = lp.ss.pi;
             info.lightN = lp.ss.n;

@@ -132,6 +132,10 @@ class RenderScene:
             lights[i] = capi.Light(max(int(li[0]), 0), max(int(li[1]), 0), int(li[2]), float(lf[0]), int(li[3]),
                                    float(lf[1]), float(lf[2]), float(lf[3]), float(lf[4]), float(lf[5]), int(li[4]),
                                    ltype)
+        if "lights_geom" in d:  # point / spot / distant lights: their placement (b200pt_render_desc::light_geometry)
+            geom = np.ascontiguousarray(d["lights_geom"], np.float32).reshape(nl, capi.LIGHT_GEOMETRY_FLOATS)
+            keep.append(geom)
+            r.light_geometry = geom.ctypes.data_as(C.POINTER(C.c_float))
         meshes = (capi.MeshAttr * max(nme, 1))()
         # per-corner normals / uv: the meshes that have them take their 3 * ntris rows from corner_n / corner_uv in order
         has_n = d["mesh_has_n"] if "mesh_has_n" in d else np.zeros(nme, np.uint32)

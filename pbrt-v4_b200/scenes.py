@@ -361,6 +361,16 @@ MATERIALS = {
 }
 
 
+# LightSource lines for cornell_pbrt / config5_pbrt (lights=...): the delta lights (lights.h: PointLight 189-239,
+# SpotLight 747-801, DistantLight 242-297).  The distant light shines in through the room's open front.
+LIGHTS = {
+    "point": 'LightSource "point" "point3 from" [0.3 0.72 0.4] "rgb I" [0.5 0.4 0.25]',
+    "spot": 'LightSource "spot" "point3 from" [0.85 0.9 0.15] "point3 to" [0.4 0 0.6] "float coneangle" 35 '
+            '"float conedeltaangle" 12 "rgb I" [2 2.2 3]',
+    "distant": 'LightSource "distant" "point3 from" [0.2 1.3 -1.5] "point3 to" [0.6 0.2 0.5] "rgb L" [0.9 0.8 0.6]',
+}
+
+
 # GBufferFilm, the ISET spectral film (film.cpp:1053-1106): 31 radiance channels + the AOV groups built here; the
 # channel order of its image is R G B, Radiance.C01-31, P.X-Z, MaterialId, InstanceId, Ns.X-Z, N.X-Z, Variance.R-B,
 # RelativeVariance.R-B (film.cpp:766-831)
@@ -376,7 +386,7 @@ def _gbuffer_film(out, xres, yres):
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
                  boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
-                 film="rgb", nbuckets=31, patches=False, smooth=False, alpha=False):
+                 film="rgb", nbuckets=31, patches=False, smooth=False, alpha=False, lights=()):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -432,6 +442,8 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
         # alpha: the tall box is a stochastic cut-out (constant alpha 0.5), cpu/primitive.cpp:57-70
         lines.append('  ' + _mesh_pbrt(m) + (' "float alpha" 0.5' if alpha and k == 6 else ''))
         lines.append('AttributeEnd')
+    for name in lights:  # LIGHTS names or LightSource lines
+        lines += ['AttributeBegin', '  ' + LIGHTS.get(name, name), 'AttributeEnd']
     if many_lights:
         # config 3's "many-light" mechanism at test size: small one-sided emissive quads of varied power,
         # position and orientation inside the box (what the light BVH's importance has to tell apart)
@@ -878,7 +890,7 @@ def with_density_grid(d, density, medium=0):
 
 
 def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm", seed=0, grid=256, density=None,
-                 fog=True, crop=None, lightsampler="bvh", patch_cap=False):
+                 fog=True, crop=None, lightsampler="bvh", patch_cap=False, lights=()):
     """BASELINE configs[4]: VolPathIntegrator in the Cornell room: a thin homogeneous fog fills the room (an
     `interface` quad closes the open front; the camera stays in vacuum: a camera medium trips a race in the
     reference's BasicScene::GetMedium / CreateMedia, scene.cpp:809-850), and a box-shaped `interface` shell
@@ -930,6 +942,8 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
             lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
         lines.append('  ' + _mesh_pbrt(m))
         lines.append('AttributeEnd')
+    for name in lights:  # LIGHTS names or LightSource lines; inside the room, so in the fog
+        lines += ['AttributeBegin', f'  MediumInterface {outside} {outside}', '  ' + LIGHTS.get(name, name), 'AttributeEnd']
     # the shell: interface material (no BSDF), cloud inside, fog (or vacuum) outside; slightly larger than
     # the grid's box so every ray segment inside the shell sees the whole grid
     e = 0.004

@@ -206,6 +206,13 @@ TIGHT_CASES = {
     # DiffuseTransmissionMaterial: one with the default scale, one whose scale pushes T into the clamp
     "tight_dtrans": ("cornell", dict(res=32, spp=4096, maxdepth=5,
                                      boxes=("diffuse_transmission", "diffuse_transmission_scaled"))),
+    # PointLight, SpotLight, DistantLight beside the ceiling emitter: under the BVH light sampler (point and
+    # spot in the tree, the distant one in its list of unbounded lights), under the power sampler, and in the fogged
+    # room of config 5 (VolPathIntegrator: shadow rays through the fog, the cloud and the front cap)
+    "tight_lights": ("cornell", dict(res=32, spp=4096, maxdepth=5, lightsampler="bvh", lights=("point", "spot", "distant"),
+                                     boxes=(None, "conductor_rough"))),
+    "tight_lights_power": ("cornell", dict(res=32, spp=4096, maxdepth=4, lightsampler="power", lights=("point", "spot", "distant"))),
+    "tight_lights_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=8192, lights=("point", "spot", "distant"))),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),
 }

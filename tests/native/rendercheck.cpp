@@ -127,6 +127,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.lightBvhNodes = rh.lightBvhNodes.data();
     rs.lightBitTrails = rh.lightBitTrails.data();
     rs.infiniteLights = rh.infiniteLights.data();
+    rs.lightGeom = rh.lightGeom.empty() ? nullptr : rh.lightGeom.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
@@ -186,6 +187,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.lightBvhNodes = rh.lightBvhNodes.data();
     rs.lightBitTrails = rh.lightBitTrails.data();
     rs.infiniteLights = rh.infiniteLights.data();
+    rs.lightGeom = rh.lightGeom.empty() ? nullptr : rh.lightGeom.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
