@@ -291,7 +291,8 @@ typedef struct b200pt_render_desc {
     float imaging_ratio, max_component_value;
     float output_rgb_from_sensor_rgb[9];
     int32_t sensor_spectrum[3]; /* r_bar g_bar b_bar */
-    /* sampler: 0 = ZSobol (samplers.h:224-370) */
+    /* sampler: B200PT_SAMPLER_ZSOBOL (samplers.h:224-370) or B200PT_SAMPLER_INDEPENDENT (samplers.h:442-476: one PCG32
+     * stream per pixel; `randomize` is unused) */
     uint32_t sampler_type;
     int32_t samples_per_pixel, seed;
     uint32_t randomize; /* 0 none 1 permutedigits 2 fastowen 3 owen */
@@ -371,9 +372,12 @@ typedef struct b200pt_render_desc {
     float gbuffer_output_from_render[16];
     float gbuffer_output_from_render_inv[16];
     const int32_t *material_ids;
-    /* the film's pixel filter (filters.h): only B200PT_FILTER_BOX (BoxFilter, filters.h:37-77, radius = filter_radius:
-     * uniform sample offsets, weight 1) is implemented; any other value is refused with B200PT_ERR_INVALID - pbrt's
-     * default is the Gaussian, a host adaptor must say so instead of getting a box-filtered image silently. */
+    /* the film's pixel filter (filters.h).  B200PT_FILTER_BOX (BoxFilter, filters.h:37-77, radius = filter_radius):
+     * uniform sample offsets, weight 1.  The filters the reference samples through a FilterSampler (Gaussian, Mitchell,
+     * LanczosSinc; filters.h:80-230, filters.cpp:92-118) need filter_table: the host's tabulation of Filter::Evaluate
+     * at the centres of filter_table_size[0] x filter_table_size[1] cells over [-radius, radius]^2, row-major with x
+     * fastest (FilterSampler::f: int(32 * radius) cells per axis) - the sampling distribution is built from it as
+     * the reference builds its PiecewiseConstant2D.  B200PT_FILTER_TRIANGLE (its own analytic Sample) is refused. */
     uint32_t filter_type;
     /* placement of the delta lights, B200PT_LIGHT_GEOMETRY_FLOATS floats per light for ALL n_lights lights (rows of
      * other light types are ignored); NULL when the scene has none.  Row: [0..2] point / spot: renderFromLight(0,0,0)
@@ -381,8 +385,11 @@ typedef struct b200pt_render_desc {
      * (DistantLight::Preprocess, lights.h:277-279); [4..12] spot: upper 3 x 3 of renderFromLight's inverse, row major
      * (lights.h:790); [13] spot cosFalloffStart, [14] spot cosFalloffEnd (lights.cpp:1376-1385); [15] 0. */
     const float *light_geometry;
+    const float *filter_table; /* see filter_type; NULL for the box filter */
+    int32_t filter_table_size[2];
 } b200pt_render_desc;
 #define B200PT_LIGHT_GEOMETRY_FLOATS 16
+enum { B200PT_SAMPLER_ZSOBOL = 0, B200PT_SAMPLER_INDEPENDENT = 1 };
 enum { B200PT_FILTER_BOX = 0, B200PT_FILTER_GAUSSIAN = 1, B200PT_FILTER_MITCHELL = 2, B200PT_FILTER_SINC = 3, B200PT_FILTER_TRIANGLE = 4 };
 
 typedef struct b200pt_render b200pt_render;

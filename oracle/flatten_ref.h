@@ -236,6 +236,16 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         const uint32_t ft = rf->filter.template Is<BoxFilter>() ? 0u : rf->filter.template Is<GaussianFilter>() ? 1u
                           : rf->filter.template Is<MitchellFilter>() ? 2u : rf->filter.template Is<LanczosSincFilter>() ? 3u : 4u;
         w.u32("filter_type", {1}, {ft});
+        // the filters sampled through a FilterSampler: its tabulated function (filters.cpp:92-118), [ny][nx]
+        auto dumpTable = [&](const FilterSampler &fs) {
+            std::vector<float> tab;
+            for (int y = 0; y < fs.f.YSize(); ++y)
+                for (int x = 0; x < fs.f.XSize(); ++x) tab.push_back(fs.f(x, y));
+            w.f32("filter_table", {uint32_t(fs.f.YSize()), uint32_t(fs.f.XSize())}, tab);
+        };
+        if (ft == 1) dumpTable(rf->filter.template Cast<GaussianFilter>()->sampler);
+        if (ft == 2) dumpTable(rf->filter.template Cast<MitchellFilter>()->sampler);
+        if (ft == 3) dumpTable(rf->filter.template Cast<LanczosSincFilter>()->sampler);
         Vector2f fr = rf->filter.Radius();
         w.f32("film_params", {4}, {fr.x, fr.y, rf->sensor->imagingRatio, rf->maxComponentValue});
         std::vector<float> om(9);
@@ -275,8 +285,11 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         const ZSobolSampler *zs = sampler.Cast<ZSobolSampler>();
         w.i32("sampler", {6}, {0, 1 << zs->log2SamplesPerPixel, zs->seed, int(zs->randomize),
                                zs->log2SamplesPerPixel, zs->nBase4Digits});
+    } else if (sampler.Is<IndependentSampler>()) {
+        const IndependentSampler *is = sampler.Cast<IndependentSampler>();
+        w.i32("sampler", {6}, {1, is->samplesPerPixel, is->seed, 0, 0, 0});
     } else
-        die("only the zsobol sampler is dumped so far");
+        die("only the zsobol and independent samplers are dumped so far");
 
     // ---- integrator parameters (cpu/integrators.cpp PathIntegrator::Create)
     int maxDepth = integratorParams.GetOneInt("maxdepth", 5);

@@ -39,6 +39,7 @@ struct Table {
     std::vector<uint32_t> dims;
     std::vector<uint32_t> words;
     size_t rows() const { return dims.empty() ? 0 : dims[0]; }
+    size_t cols() const { return dims.size() < 2 ? 1 : dims[1]; }
     const float *f() const { return reinterpret_cast<const float *>(words.data()); }
     const int32_t *i() const { return reinterpret_cast<const int32_t *>(words.data()); }
     const uint32_t *u() const { return words.data(); }
@@ -184,6 +185,12 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
     memcpy(r.full_resolution, fi + 4, 8);
     const float *fp = T.at("film_params").f();
     r.filter_type = T.has("filter_type") ? T.at("filter_type").u()[0] : 0;
+    if (T.has("filter_table")) {
+        const Table &ft = T.at("filter_table");
+        r.filter_table = ft.f();
+        r.filter_table_size[0] = int32_t(ft.cols());
+        r.filter_table_size[1] = int32_t(ft.rows());
+    }
     r.filter_radius[0] = fp[0];
     r.filter_radius[1] = fp[1];
     r.imaging_ratio = fp[2];

@@ -186,7 +186,8 @@ class RenderDesc(C.Structure):
                 ("microlens_simulation_radius", C.c_int32),
                 ("gbuffer_output_from_render", C.c_float * 16), ("gbuffer_output_from_render_inv", C.c_float * 16),
                 ("material_ids", C.POINTER(C.c_int32)), ("filter_type", C.c_uint32),
-                ("light_geometry", C.POINTER(C.c_float))]
+                ("light_geometry", C.POINTER(C.c_float)),
+                ("filter_table", C.POINTER(C.c_float)), ("filter_table_size", C.c_int32 * 2)]
 
 
 GBUFFER_RADIANCE, GBUFFER_POSITION, GBUFFER_MATERIAL, GBUFFER_INSTANCE = 1, 2, 4, 8

@@ -270,6 +270,7 @@ GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nA
     if (pb.aov) pb.aov[i] = 0.f;  // no VisibleSurface yet
     StoreHeader(pb, i, p);
     pb.scalars[kCameraWeightScalar * n + i] = p.cameraWeight;
+    pb.scalars[kFilterWeightScalar * n + i] = p.filterWeight;
     // a sample without a camera ray (vignetted by the lens system) keeps its queue slot with a ray that
     // hits nothing (tMax < 0); the classify kernel drops it
     StoreRay(pb.rays[0], i, p.rayO, p.rayD, p.rayTMax);
@@ -644,7 +645,8 @@ FinishKernel(RenderSceneDev rs, PassBuffers pb, int nActive) {
     const float *L = pb.L + i;
     float rgbw[4];
     const float cw = pb.scalars[kCameraWeightScalar * n + i];
-    FinishPath(rs, pb.scalars[i], (uint32_t)pb.ints[3 * n + i], 1.f, [&](int k) { return cw * L[k * n]; }, rgbw);
+    FinishPath(rs, pb.scalars[i], (uint32_t)pb.ints[3 * n + i], pb.scalars[kFilterWeightScalar * n + i],
+               [&](int k) { return cw * L[k * n]; }, rgbw);
     reinterpret_cast<float4 *>(pb.rgbw)[i] = make_float4(rgbw[0], rgbw[1], rgbw[2], rgbw[3]);
 }
 
@@ -679,7 +681,7 @@ __global__ void FilmAddSpectralKernel(FilmDev fd, PassBuffers pb, int nPixels, i
         long long path = (long long)s * nPixels + pix;
         const float *L = pb.L + path;
         const float cw = pb.scalars[kCameraWeightScalar * n + path];
-        SpectralFilmAdd(fd, pb.scalars[path], 1.f, [&](int k) { return cw * L[k * n]; },
+        SpectralFilmAdd(fd, pb.scalars[path], pb.scalars[kFilterWeightScalar * n + path], [&](int k) { return cw * L[k * n]; },
                         [&](int b, float v, float w) {
                             bucketSums[(long long)b * nPixels] += v;
                             if (fd.type == 1) weightSums[(long long)b * nPixels] += w;  // (GBufferFilm never reads them)

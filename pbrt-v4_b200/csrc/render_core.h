@@ -14,11 +14,16 @@
 namespace b200pt {
 
 // ------------------------------------------------------------------ ZSobol sampler (samplers.h:224-370)
+// `independent`: the same object is the IndependentSampler (samplers.h:442-476) - a PCG32 stream per pixel, set to
+// draw number sampleIndex * 65536 + dimension; every value is one draw, so `dimension` (the count the path state
+// keeps, as for ZSobol) is all it takes to pick the stream up again in the next kernel.
 struct ZSobol {
     int log2Spp, nBase4Digits, seed;
     uint32_t randomize;
     uint64_t mortonIndex;
     int dimension;
+    bool independent;
+    PCG32 rng;
 };
 
 B2_HD uint64_t LeftShift2(uint64_t x) {  // util/math.h:83-91
@@ -38,6 +43,18 @@ B2_HD void ZSobolStart(ZSobol &s, const SamplerDev &sd, int px, int py, int inde
     s.seed = sd.seed;
     s.randomize = sd.randomize;
     s.dimension = dim;
+    s.independent = sd.type == 1;
+    if (s.independent) {  // IndependentSampler::StartPixelSample (samplers.h:457-460)
+        unsigned char buf[12];  // Hash(Point2i p, int seed)
+        memcpy(buf, &px, 4);
+        memcpy(buf + 4, &py, 4);
+        memcpy(buf + 8, &sd.seed, 4);
+        uint64_t seq = Murmur64A(buf, 12, 0);
+        s.rng = PcgSeed(seq, MixBits(seq));
+        PcgAdvance(s.rng, uint64_t(index) * 65536ull + uint64_t(dim));
+        s.mortonIndex = 0;
+        return;
+    }
     s.mortonIndex = (EncodeMorton2(px, py) << sd.log2Spp) | (uint64_t)index;
 }
 
@@ -126,17 +143,69 @@ B2_HD float SobolSampleZ(uint64_t a, int dim, uint32_t randomize, uint32_t hash)
     return fminf(v * 0x1p-32f, kOneMinusEps);
 }
 B2_HD_NOINLINE float ZSobolGet1D(ZSobol &s) {  // samplers.h:258-272
+    if (s.independent) {  // rng.Uniform<Float>() (util/rng.h:120-123)
+        ++s.dimension;
+        return fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
+    }
     uint64_t idx = ZSobolSampleIndex(s);
     ++s.dimension;
     uint32_t h = (uint32_t)Hash2i(s.dimension, s.seed);
     return SobolSampleZ(idx, 0, s.randomize, h);
 }
 B2_HD_NOINLINE void ZSobolGet2D(ZSobol &s, float &u0, float &u1) {  // samplers.h:274-293
+    if (s.independent) {
+        s.dimension += 2;
+        u0 = fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
+        u1 = fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
+        return;
+    }
     uint64_t idx = ZSobolSampleIndex(s);
     s.dimension += 2;
     uint64_t bits = Hash2i(s.dimension, s.seed);
     u0 = SobolSampleZ(idx, 0, s.randomize, (uint32_t)bits);
     u1 = SobolSampleZ(idx, 1, s.randomize, (uint32_t)(bits >> 32));
+}
+
+// ------------------------------------------------------------------ pixel filter
+// FindInterval (util/math.h:509-520) over cdf[0..sz-1] with the predicate cdf[i] <= u
+B2_HD int FindCdfInterval(const float *cdf, int sz, float u) {
+    int size = sz - 2, first = 1;
+    while (size > 0) {
+        int half = size >> 1, middle = first + half;
+        bool pred = cdf[middle] <= u;
+        first = pred ? middle + 1 : first;
+        size = pred ? size - (half + 1) : half;
+    }
+    int o = first - 1;
+    return o < 0 ? 0 : (o > sz - 2 ? sz - 2 : o);
+}
+// PiecewiseConstant1D::Sample (util/sampling.h:657-675) over n cells of [lo, hi]; returns x, *offset the cell
+B2_HD float SamplePiecewise1D(const float *cdf, int n, float lo, float hi, float u, int *offset) {
+    int o = FindCdfInterval(cdf, n + 1, u);
+    *offset = o;
+    float du = u - cdf[o];
+    if (cdf[o + 1] - cdf[o] > 0) du /= cdf[o + 1] - cdf[o];
+    return Lerp((o + du) / n, lo, hi);
+}
+// Filter::Sample(u): BoxFilter (filters.h:60-64), or FilterSampler::Sample (filters.h:27-33): the point from the
+// tabulated distribution (PiecewiseConstant2D::Sample, util/sampling.h:752-762), weight f[cell] / pdf
+B2_HD void SampleFilter(const FilmDev &film, float u0, float u1, float &fx, float &fy, float &weight) {
+    if (film.filterType == 0) {
+        fx = Lerp(u0, -film.filterRadiusX, film.filterRadiusX);
+        fy = Lerp(u1, -film.filterRadiusY, film.filterRadiusY);
+        weight = 1.f;
+        return;
+    }
+    const int nx = film.filterNx, ny = film.filterNy;
+    const float *f = film.filterTable, *condCdf = f + nx * ny, *condInt = condCdf + ny * (nx + 1);
+    const float *margCdf = condInt + ny, margInt = margCdf[ny + 1];
+    int iv, iu;
+    fy = SamplePiecewise1D(margCdf, ny, -film.filterRadiusY, film.filterRadiusY, u1, &iv);
+    float pdf1 = margInt > 0 ? condInt[iv] / margInt : 0.f;
+    fx = SamplePiecewise1D(condCdf + iv * (nx + 1), nx, -film.filterRadiusX, film.filterRadiusX, u0, &iu);
+    float fv = f[iv * nx + iu];
+    float pdf0 = condInt[iv] > 0 ? fabsf(fv) / condInt[iv] : 0.f;
+    weight = fv / (pdf0 * pdf1);
 }
 
 // ------------------------------------------------------------------ wavelengths and spectra

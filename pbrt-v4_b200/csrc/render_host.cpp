@@ -43,8 +43,31 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("omni camera: microlens simulation radius must be 0..8");
         }
     }
-    if (d->filter_type != B200PT_FILTER_BOX)
-        return bad("unsupported pixel filter: only the box filter is implemented (filter_type)");
+    if (d->filter_type == B200PT_FILTER_TRIANGLE || d->filter_type > B200PT_FILTER_SINC)
+        return bad("unsupported pixel filter: box, and gaussian / mitchell / sinc through filter_table, are implemented");
+    if (d->filter_type != B200PT_FILTER_BOX) {
+        const int nx = d->filter_table_size[0], ny = d->filter_table_size[1];
+        if (!d->filter_table || nx < 1 || ny < 1 || nx > 4096 || ny > 4096)
+            return bad("filter_type needs filter_table (the tabulated filter function) and its size");
+        if (!(d->filter_radius[0] > 0) || !(d->filter_radius[1] > 0)) return bad("filter radius must be positive");
+        for (int i = 0; i < nx * ny; ++i)
+            if (!std::isfinite(d->filter_table[i])) return bad("filter_table holds a non-finite value");
+        // PiecewiseConstant2D(f, domain) (util/sampling.h:731-747) out of PiecewiseConstant1D's (:625-649), in float as there
+        std::vector<float> &t = out.filterTable;
+        t.assign(size_t(nx) * ny + size_t(ny) * (nx + 1) + ny + (ny + 1) + 1, 0.f);
+        std::copy(d->filter_table, d->filter_table + size_t(nx) * ny, t.begin());
+        float *condCdf = t.data() + size_t(nx) * ny, *condInt = condCdf + size_t(ny) * (nx + 1), *margCdf = condInt + ny;
+        auto build = [](const float *func, int n, float lo, float hi, float *cdf) {  // returns funcInt
+            cdf[0] = 0;
+            for (int i = 1; i < n + 1; ++i) cdf[i] = cdf[i - 1] + std::abs(func[i - 1]) * (hi - lo) / n;
+            float funcInt = cdf[n];
+            for (int i = 1; i < n + 1; ++i) cdf[i] = funcInt == 0 ? float(i) / float(n) : cdf[i] / funcInt;
+            return funcInt;
+        };
+        for (int v = 0; v < ny; ++v)
+            condInt[v] = build(d->filter_table + size_t(v) * nx, nx, -d->filter_radius[0], d->filter_radius[0], condCdf + size_t(v) * (nx + 1));
+        margCdf[ny + 1] = build(condInt, ny, -d->filter_radius[1], d->filter_radius[1], margCdf);
+    }
     if (d->film_type > 2) return bad("unsupported film type");
     if (d->film_type == 2 && (d->n_buckets != 31 || d->lambda_min != 395.f || d->lambda_max != 705.f))
         return bad("gbuffer film: 31 buckets over 395..705 nm (hard-coded in the reference, film.h:383-389)");
@@ -53,7 +76,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         if (d->lambda_min != 395.f || d->lambda_max != 705.f)
             return bad("spectral film: lambda_min / lambda_max must be 395 / 705 nm (the build's sampled range)");
     }
-    if (d->sampler_type != 0) return bad("unsupported sampler type");
+    if (d->sampler_type > B200PT_SAMPLER_INDEPENDENT) return bad("unsupported sampler type (zsobol and independent are implemented)");
     if (d->light_sampler > 2) return bad("unsupported light sampler (uniform, power and bvh are implemented)");
     if (d->light_sampler == 2 && d->n_lights && (!d->light_bit_trails || (d->n_light_bvh_nodes && !d->light_bvh_nodes)))
         return bad("the bvh light sampler needs light_bvh_nodes and light_bit_trails");
@@ -125,7 +148,10 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     rs.film.y1 = d->pixel_bounds[3];
     rs.film.fullResX = d->full_resolution[0];
     rs.film.fullResY = d->full_resolution[1];
-    rs.film.filterType = 0;
+    rs.film.filterType = d->filter_type;
+    rs.film.filterNx = d->filter_type ? d->filter_table_size[0] : 0;
+    rs.film.filterNy = d->filter_type ? d->filter_table_size[1] : 0;
+    rs.film.filterTable = nullptr;  // filled by the owner of the storage
     rs.film.filterRadiusX = d->filter_radius[0];
     rs.film.filterRadiusY = d->filter_radius[1];
     rs.film.imagingRatio = d->imaging_ratio;
@@ -133,7 +159,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     std::memcpy(rs.film.outputRGBFromSensorRGB, d->output_rgb_from_sensor_rgb, 36);
     for (int c = 0; c < 3; ++c) rs.film.sensorSpectrum[c] = d->sensor_spectrum[c];
     // ZSobolSampler constructor (samplers.h:228-238)
-    rs.sampler.type = 0;
+    rs.sampler.type = d->sampler_type;  // 1: IndependentSampler, which only uses samplesPerPixel and seed
     rs.sampler.samplesPerPixel = d->samples_per_pixel;
     rs.sampler.seed = d->seed;
     rs.sampler.randomize = d->randomize;

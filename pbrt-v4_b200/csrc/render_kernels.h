@@ -8,7 +8,8 @@
 
 namespace b200pt {
 
-constexpr int kPathScalars = 16;  // lambdaU, etaScale, pB, prev{pi.lo, pi.hi, n, ns}, cameraWeight
+constexpr int kPathScalars = 17;  // lambdaU, etaScale, pB, prev{pi.lo, pi.hi, n, ns}, cameraWeight, filterWeight
+constexpr int kFilterWeightScalar = 16;  // FilterSample::weight of the camera sample (1 for the box filter)
 constexpr int kCameraWeightScalar = 15;  // written by the generate kernel, read when the sample is finished
 constexpr int kPathInts = 5;      // sampleIndex, dimension, depth, flags, medium
 constexpr int kShadowAuxWords = 20;  // volpath light sample: p_l, scatterPDF, medium, started, rng[4], lightPi[6], lightN[3]

@@ -14,31 +14,8 @@
 
 namespace b200pt {
 
-// MurmurHash64A over a short buffer (util/hash.h:18-68) and Hash(args...) (:95-103) for the argument
-// packs LayeredBxDF uses: (int seed, Vector3f), (Vector3f), (Float, Point2f).
-B2_HD uint64_t Murmur64A(const unsigned char *key, size_t len, uint64_t seed) {
-    const uint64_t m = 0xc6a4a7935bd1e995ull;
-    const int r = 47;
-    uint64_t h = seed ^ (len * m);
-    size_t nblocks = len / 8;
-    for (size_t i = 0; i < nblocks; ++i) {
-        uint64_t k;
-        memcpy(&k, key + 8 * i, 8);
-        k *= m;
-        k ^= k >> r;
-        k *= m;
-        h ^= k;
-        h *= m;
-    }
-    const unsigned char *tail = key + 8 * nblocks;
-    int rem = (int)(len & 7);
-    for (int i = rem - 1; i >= 0; --i) h ^= uint64_t(tail[i]) << (8 * i);
-    if (rem) h *= m;
-    h ^= h >> r;
-    h *= m;
-    h ^= h >> r;
-    return h;
-}
+// Hash(args...) (util/hash.h:95-103) for the argument packs LayeredBxDF uses: (int seed, Vector3f), (Vector3f),
+// (Float, Point2f); Murmur64A and the PCG32 generator are in render_math.h
 B2_HD uint64_t HashSeedV3(int32_t seed, V3 v) {
     unsigned char buf[16];
     memcpy(buf, &seed, 4);
@@ -55,25 +32,6 @@ B2_HD uint64_t Hash3f(float a, float b, float c) {
     return Murmur64A(buf, 12, 0);
 }
 
-struct PCG32 {  // util/rng.h:30-135
-    uint64_t state, inc;
-};
-B2_HD uint32_t PcgNext(PCG32 &g) {
-    uint64_t oldstate = g.state;
-    g.state = oldstate * 0x5851f42d4c957f2dull + g.inc;
-    uint32_t xorshifted = (uint32_t)(((oldstate >> 18u) ^ oldstate) >> 27u);
-    uint32_t rot = (uint32_t)(oldstate >> 59u);
-    return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
-}
-B2_HD PCG32 PcgSeed(uint64_t sequenceIndex, uint64_t seed) {
-    PCG32 g;
-    g.state = 0u;
-    g.inc = (sequenceIndex << 1u) | 1u;
-    PcgNext(g);
-    g.state += seed;
-    PcgNext(g);
-    return g;
-}
 // the `r` lambda of LayeredBxDF: min(rng.Uniform<Float>(), OneMinusEpsilon)
 B2_HD float PcgFloat(PCG32 &g) { return fminf(kOneMinusEps, PcgNext(g) * 0x1p-32f); }
 

@@ -151,6 +151,65 @@ B2_HD uint64_t Hash2i(int32_t a, int32_t b) {
     return h;
 }
 
+// MurmurHash64A over a short buffer (util/hash.h:18-68) and Hash(args...) (:95-103) for the argument
+// packs LayeredBxDF uses: (int seed, Vector3f), (Vector3f), (Float, Point2f).
+B2_HD uint64_t Murmur64A(const unsigned char *key, size_t len, uint64_t seed) {
+    const uint64_t m = 0xc6a4a7935bd1e995ull;
+    const int r = 47;
+    uint64_t h = seed ^ (len * m);
+    size_t nblocks = len / 8;
+    for (size_t i = 0; i < nblocks; ++i) {
+        uint64_t k;
+        memcpy(&k, key + 8 * i, 8);
+        k *= m;
+        k ^= k >> r;
+        k *= m;
+        h ^= k;
+        h *= m;
+    }
+    const unsigned char *tail = key + 8 * nblocks;
+    int rem = (int)(len & 7);
+    for (int i = rem - 1; i >= 0; --i) h ^= uint64_t(tail[i]) << (8 * i);
+    if (rem) h *= m;
+    h ^= h >> r;
+    h *= m;
+    h ^= h >> r;
+    return h;
+}
+struct PCG32 {  // util/rng.h:30-135
+    uint64_t state, inc;
+};
+B2_HD uint32_t PcgNext(PCG32 &g) {
+    uint64_t oldstate = g.state;
+    g.state = oldstate * 0x5851f42d4c957f2dull + g.inc;
+    uint32_t xorshifted = (uint32_t)(((oldstate >> 18u) ^ oldstate) >> 27u);
+    uint32_t rot = (uint32_t)(oldstate >> 59u);
+    return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+}
+B2_HD PCG32 PcgSeed(uint64_t sequenceIndex, uint64_t seed) {
+    PCG32 g;
+    g.state = 0u;
+    g.inc = (sequenceIndex << 1u) | 1u;
+    PcgNext(g);
+    g.state += seed;
+    PcgNext(g);
+    return g;
+}
+// RNG::Advance (util/rng.h:137-150): the generator's state `idelta` draws on, in O(log idelta)
+B2_HD void PcgAdvance(PCG32 &g, uint64_t delta) {
+    uint64_t curMult = 0x5851f42d4c957f2dull, curPlus = g.inc, accMult = 1u, accPlus = 0u;
+    while (delta > 0) {
+        if (delta & 1) {
+            accMult *= curMult;
+            accPlus = accPlus * curMult + curPlus;
+        }
+        curPlus = (curMult + 1) * curPlus;
+        curMult *= curMult;
+        delta /= 2;
+    }
+    g.state = accMult * g.state + accPlus;
+}
+
 B2_HD uint32_t ReverseBits32(uint32_t n) {
 #if defined(__CUDA_ARCH__)
     return __brev(n);

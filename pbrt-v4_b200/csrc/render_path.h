@@ -77,10 +77,8 @@ B2_HD void GenerateCameraPath(const RenderSceneDev &rs, PathRegs &p, int px, int
     p.lambdaU = ZSobolGet1D(s);
     float f0, f1;
     ZSobolGet2D(s, f0, f1);  // GetPixel2D -> filter.Sample
-    // BoxFilter::Sample (filters.h): p = Lerp(u, -radius, radius), weight 1
-    float fx = Lerp(f0, -rs.film.filterRadiusX, rs.film.filterRadiusX);
-    float fy = Lerp(f1, -rs.film.filterRadiusY, rs.film.filterRadiusY);
-    p.filterWeight = 1.f;
+    float fx, fy;
+    SampleFilter(rs.film, f0, f1, fx, fy, p.filterWeight);
     float pFilmX = px + fx + 0.5f, pFilmY = py + fy + 0.5f;
     (void)ZSobolGet1D(s);  // time
     float l0, l1;

@@ -101,8 +101,12 @@ struct FilmDev {
     int32_t nBuckets;            // spectral film
     int32_t x0, y0, x1, y1;      // pixelBounds
     int32_t fullResX, fullResY;
-    uint32_t filterType;         // 0 box
+    uint32_t filterType;         // 0 box; otherwise sampled through filterTable (FilterSampler, filters.cpp:92-118)
     float filterRadiusX, filterRadiusY;
+    // FilterSampler: the tabulated filter function and its PiecewiseConstant2D over [-radius, radius]^2, one array:
+    // f[ny][nx] | conditional cdf[ny][nx + 1] | conditional funcInt[ny] | marginal cdf[ny + 1] | marginal funcInt
+    int32_t filterNx, filterNy;
+    const float *filterTable;
     float imagingRatio;
     float maxComponentValue;
     float outputRGBFromSensorRGB[9];

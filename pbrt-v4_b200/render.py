@@ -108,6 +108,11 @@ class RenderScene:
         r.full_resolution[:] = [int(x) for x in d["film_ints"][4:6]]
         r.filter_radius[:] = [float(x) for x in d["film_params"][:2]]
         r.filter_type = int(d["filter_type"][0]) if "filter_type" in d else 0  # 0 = box (older dumps: box only)
+        if "filter_table" in d:  # FilterSampler::f of the gaussian / mitchell / sinc filters, [ny, nx]
+            ft = np.ascontiguousarray(d["filter_table"], np.float32)
+            keep.append(ft)
+            r.filter_table = ft.ctypes.data_as(C.POINTER(C.c_float))
+            r.filter_table_size[:] = [ft.shape[1], ft.shape[0]]
         r.imaging_ratio, r.max_component_value = float(d["film_params"][2]), float(d["film_params"][3])
         r.output_rgb_from_sensor_rgb[:] = [float(x) for x in d["film_matrix"]]
         r.sensor_spectrum[:] = [int(x) for x in d["film_sensor"]]

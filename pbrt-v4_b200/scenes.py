@@ -386,7 +386,8 @@ def _gbuffer_film(out, xres, yres):
 
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
                  boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
-                 film="rgb", nbuckets=31, patches=False, smooth=False, alpha=False, lights=()):
+                 film="rgb", nbuckets=31, patches=False, smooth=False, alpha=False, lights=(), sampler="zsobol",
+                 pixelfilter="box"):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -396,10 +397,10 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
     lines = [
         'LookAt 0.5 0.5 -1.4  0.5 0.5 0.5  0 1 0',
         'Camera "perspective" "float fov" 39.3',
-        f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
+        f'Sampler "{sampler}" "integer pixelsamples" {spp} "integer seed" {seed}',
         f'Integrator "path" "integer maxdepth" {maxdepth} "string lightsampler" "{lightsampler}"'
         + (' "bool regularize" true' if regularize else ''),
-        'PixelFilter "box"',
+        'PixelFilter ' + (pixelfilter if pixelfilter.startswith('"') else f'"{pixelfilter}"'),  # a name, or name + parameters
         (f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false'
          if film == "rgb" else
          _gbuffer_film(out, res, res) if film == "gbuffer" else
@@ -890,7 +891,7 @@ def with_density_grid(d, density, medium=0):
 
 
 def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm", seed=0, grid=256, density=None,
-                 fog=True, crop=None, lightsampler="bvh", patch_cap=False, lights=()):
+                 fog=True, crop=None, lightsampler="bvh", patch_cap=False, lights=(), sampler="zsobol"):
     """BASELINE configs[4]: VolPathIntegrator in the Cornell room: a thin homogeneous fog fills the room (an
     `interface` quad closes the open front; the camera stays in vacuum: a camera medium trips a race in the
     reference's BasicScene::GetMedium / CreateMedia, scene.cpp:809-850), and a box-shaped `interface` shell
@@ -904,7 +905,7 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
     lines = ['LookAt 0.5 0.5 -1.4  0.5 0.5 0.5  0 1 0']
     lines += [
         'Camera "perspective" "float fov" 39.3',
-        f'Sampler "zsobol" "integer pixelsamples" {spp} "integer seed" {seed}',
+        f'Sampler "{sampler}" "integer pixelsamples" {spp} "integer seed" {seed}',
         f'Integrator "volpath" "integer maxdepth" {maxdepth} "string lightsampler" "{lightsampler}"',
         'PixelFilter "box"',
         f'Film "rgb" "string filename" "{out}" "integer xresolution" {res[0]} "integer yresolution" {res[1]} '

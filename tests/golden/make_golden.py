@@ -213,6 +213,16 @@ TIGHT_CASES = {
                                      boxes=(None, "conductor_rough"))),
     "tight_lights_power": ("cornell", dict(res=32, spp=4096, maxdepth=4, lightsampler="power", lights=("point", "spot", "distant"))),
     "tight_lights_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=8192, lights=("point", "spot", "distant"))),
+    # IndependentSampler (samplers.h:442-476), a sample count that is no power of two; surfaces with the layered
+    # model's own generators, and the volume integrator's
+    "tight_independent": ("cornell", dict(res=32, spp=9000, maxdepth=5, sampler="independent",
+                                          boxes=("coated_diffuse", "dielectric_rough"))),
+    "tight_independent_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=9000, sampler="independent")),
+    # the filters sampled through a FilterSampler (filters.cpp:92-118): pbrt's default Gaussian (radius 1.5), a Mitchell
+    # (negative lobes: negative sample weights), and a Lanczos sinc with unequal radii; 1024 spp on a 24 x 24 frame
+    "tight_gaussian": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter="gaussian")),
+    "tight_mitchell": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter='"mitchell" "float B" 0.2 "float C" 0.4')),
+    "tight_sinc": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter='"sinc" "float xradius" 3 "float yradius" 2.5')),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),
 }

@@ -128,6 +128,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.lightBitTrails = rh.lightBitTrails.data();
     rs.infiniteLights = rh.infiniteLights.data();
     rs.lightGeom = rh.lightGeom.empty() ? nullptr : rh.lightGeom.data();
+    rs.film.filterTable = rh.filterTable.empty() ? nullptr : rh.filterTable.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
@@ -188,6 +189,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.lightBitTrails = rh.lightBitTrails.data();
     rs.infiniteLights = rh.infiniteLights.data();
     rs.lightGeom = rh.lightGeom.empty() ? nullptr : rh.lightGeom.data();
+    rs.film.filterTable = rh.filterTable.empty() ? nullptr : rh.filterTable.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();

@@ -228,13 +228,23 @@ def test_golden_image_config5_volpath(P, rendercheck, name):
     assert abs(img.mean() - ref.mean()) <= TOL_MEAN * ref.mean()
 
 
+@pytest.mark.parametrize("name", ["tight_gaussian", "tight_mitchell", "tight_sinc"])
+def test_filter_sampler_filters(P, rendercheck, name):
+    """The FilterSampler filters (Gaussian, Mitchell, Lanczos sinc; filters.cpp:92-118) through the host loop over the
+    kernels' headers: the reference's paths and weights, image within rRMSE 1e-4."""
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    img = P.render.film_to_image(rendercheck(rsc), rsc.d["film_matrix"])
+    assert rrmse(img, ref) <= 1e-4, rrmse(img, ref)
+
+
 def test_majorant_grid_mirror(P):
     """scenes.majorant_grid (used to build full-size config-5 tables) reproduces the host's MajorantGrid."""
     d = P.scenes.load_b2rs(os.path.join(GOLD, "config5_small.b2rs"))
     np.testing.assert_array_equal(P.scenes.majorant_grid(d["medium_density_0"]), d["medium_majorants_0"])
 
 
-@pytest.mark.parametrize("name", ["tight_metal2", "tight_coated", "tight_alpha", "tight_glass", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power",
+@pytest.mark.parametrize("name", ["tight_metal2", "tight_coated", "tight_alpha", "tight_glass", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power", "tight_independent", "tight_independent_vol",
                                   "tight_lights_vol"])
 def test_tight_noise_gate(P, rendercheck, name):
     """The 16-spp noise-gated families at 1024-4096 spp on a 32 x 32 frame (floor 2-5 %, make_golden.py TIGHT_CASES):

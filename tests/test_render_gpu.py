@@ -260,7 +260,8 @@ def test_volume_kernels_warp_per_ray_equals_thread_per_ray(P, monkeypatch):
     assert np.array_equal(films[0], films[1])
 
 
-TIGHT = ["tight_glass", "tight_metal2", "tight_coated", "tight_alpha", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power", "tight_lights_vol", "tight_config3", "tight_config5"]
+TIGHT = ["tight_glass", "tight_metal2", "tight_coated", "tight_alpha", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power", "tight_lights_vol", "tight_independent", "tight_independent_vol",
+         "tight_config3", "tight_config5"]
 
 
 @pytest.mark.parametrize("name", TIGHT)
@@ -283,6 +284,23 @@ def test_tight_noise_gate(P, name):
     assert np.all(film[..., 3] == rsc.spp)
     assert rrmse(img, ref) <= 1.25 * floor, (rrmse(img, ref), floor)
     assert abs(img.mean() - ref.mean()) <= 0.01 * ref.mean(), (img.mean(), ref.mean())
+
+
+@pytest.mark.parametrize("name", ["tight_gaussian", "tight_mitchell", "tight_sinc"])
+def test_filter_sampler_filters(P, name):
+    """GaussianFilter (pbrt's default), MitchellFilter and LanczosSincFilter (filters.h:80-230): camera samples drawn
+    from the FilterSampler's tabulated distribution (filters.cpp:92-118), the film weighted by f / pdf - negative for the
+    lobes of the last two.  Same sampler, same paths as the reference: the diffuse Cornell box within rRMSE 1e-3."""
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img, film = r.image(), r.film()
+    finally:
+        r.close()
+    assert not np.all(film[..., 3] == rsc.spp)  # the weights are not the box filter's
+    assert rrmse(img, ref) <= 1e-3, rrmse(img, ref)
 
 
 def test_gbuffer_film_matches_reference(P):
