@@ -152,8 +152,11 @@ struct DevIO {
     int *nShadow;
     int slot;
     float *beta;  // this thread's column of the block's [31][kShadeBlock] shared array
-    __device__ DevIO(const PassBuffers &b, int pathId, int *shadowCount, float *sbeta)
-        : pb(b), path(pathId), nShadow(shadowCount), slot(-1), beta(sbeta) {}
+    float *refl;  // the same for the vertex's cached reflectance (diffuse / coated diffuse kernels; null elsewhere)
+    __device__ DevIO(const PassBuffers &b, int pathId, int *shadowCount, float *sbeta, float *srefl = nullptr)
+        : pb(b), path(pathId), nShadow(shadowCount), slot(-1), beta(sbeta), refl(srefl) {}
+    __device__ __forceinline__ float R(int k) const { return refl[k * kShadeBlock]; }
+    __device__ __forceinline__ void SetR(int k, float v) { refl[k * kShadeBlock] = v; }
     __device__ __forceinline__ float Beta(int k) const { return beta[k * kShadeBlock]; }
     __device__ __forceinline__ void SetBeta(int k, float v) { beta[k * kShadeBlock] = v; }
     __device__ __forceinline__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
@@ -345,7 +348,9 @@ ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width
     const uint2 *h = reinterpret_cast<const uint2 *>(pb.hits + 6ll * q);
     uint2 h0 = h[0], h1 = h[1], h2 = h[2];
     hit[0] = h0.x; hit[1] = h0.y; hit[2] = h1.x; hit[3] = h1.y; hit[4] = h2.x; hit[5] = h2.y;
-    DevIO io(pb, path, counts + 1, myBeta);
+    constexpr bool kCachesR = MAT == (int)MAT_DIFFUSE || MAT == (int)MAT_COATED_DIFFUSE;
+    __shared__ float srefl[kCachesR ? kNLambda * kShadeBlock : 1];
+    DevIO io(pb, path, counts + 1, myBeta, kCachesR ? srefl + threadIdx.x : nullptr);
     ShadeVertex<DevIO, MAT, LBVH, VOL, EXT>(rs, p, hit, io);
     if (p.flags & PF_ALIVE) {
         int *next = pb.counts + kCountStride * (depth + 1);

@@ -14,16 +14,11 @@
 namespace b200pt {
 
 // ------------------------------------------------------------------ ZSobol sampler (samplers.h:224-370)
-// `independent`: the same object is the IndependentSampler (samplers.h:442-476) - a PCG32 stream per pixel, set to
-// draw number sampleIndex * 65536 + dimension; every value is one draw, so `dimension` (the count the path state
-// keeps, as for ZSobol) is all it takes to pick the stream up again in the next kernel.
 struct ZSobol {
     int log2Spp, nBase4Digits, seed;
     uint32_t randomize;
     uint64_t mortonIndex;
     int dimension;
-    bool independent;
-    PCG32 rng;
 };
 
 B2_HD uint64_t LeftShift2(uint64_t x) {  // util/math.h:83-91
@@ -43,18 +38,6 @@ B2_HD void ZSobolStart(ZSobol &s, const SamplerDev &sd, int px, int py, int inde
     s.seed = sd.seed;
     s.randomize = sd.randomize;
     s.dimension = dim;
-    s.independent = sd.type == 1;
-    if (s.independent) {  // IndependentSampler::StartPixelSample (samplers.h:457-460)
-        unsigned char buf[12];  // Hash(Point2i p, int seed)
-        memcpy(buf, &px, 4);
-        memcpy(buf + 4, &py, 4);
-        memcpy(buf + 8, &sd.seed, 4);
-        uint64_t seq = Murmur64A(buf, 12, 0);
-        s.rng = PcgSeed(seq, MixBits(seq));
-        PcgAdvance(s.rng, uint64_t(index) * 65536ull + uint64_t(dim));
-        s.mortonIndex = 0;
-        return;
-    }
     s.mortonIndex = (EncodeMorton2(px, py) << sd.log2Spp) | (uint64_t)index;
 }
 
@@ -143,27 +126,60 @@ B2_HD float SobolSampleZ(uint64_t a, int dim, uint32_t randomize, uint32_t hash)
     return fminf(v * 0x1p-32f, kOneMinusEps);
 }
 B2_HD_NOINLINE float ZSobolGet1D(ZSobol &s) {  // samplers.h:258-272
-    if (s.independent) {  // rng.Uniform<Float>() (util/rng.h:120-123)
-        ++s.dimension;
-        return fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
-    }
     uint64_t idx = ZSobolSampleIndex(s);
     ++s.dimension;
     uint32_t h = (uint32_t)Hash2i(s.dimension, s.seed);
     return SobolSampleZ(idx, 0, s.randomize, h);
 }
 B2_HD_NOINLINE void ZSobolGet2D(ZSobol &s, float &u0, float &u1) {  // samplers.h:274-293
-    if (s.independent) {
-        s.dimension += 2;
-        u0 = fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
-        u1 = fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
-        return;
-    }
     uint64_t idx = ZSobolSampleIndex(s);
     s.dimension += 2;
     uint64_t bits = Hash2i(s.dimension, s.seed);
     u0 = SobolSampleZ(idx, 0, s.randomize, (uint32_t)bits);
     u1 = SobolSampleZ(idx, 1, s.randomize, (uint32_t)(bits >> 32));
+}
+
+// ------------------------------------------------------------------ the path's sampler
+// ZSobol, or the IndependentSampler (samplers.h:442-476): a PCG32 stream per pixel, set to draw number
+// sampleIndex * 65536 + dimension; every value is one draw, so the draw count the path state keeps (`dimension`, as
+// for ZSobol) is all it takes to pick the stream up again in the next kernel.  The Sobol core is what the out-of-line
+// ZSobolGet* see; `independent` stays a local, so a kernel built without the feature (EXT = 0) folds the branches.
+struct PathSampler {
+    ZSobol z;
+    bool independent;
+    PCG32 rng;
+};
+template <int EXT>
+B2_HD void PathSamplerStart(PathSampler &s, const SamplerDev &sd, int px, int py, int index, int dim) {
+    s.independent = EXT != 0 && sd.type == 1;
+    if (s.independent) {  // IndependentSampler::StartPixelSample (samplers.h:457-460)
+        unsigned char buf[12];  // Hash(Point2i p, int seed)
+        memcpy(buf, &px, 4);
+        memcpy(buf + 4, &py, 4);
+        memcpy(buf + 8, &sd.seed, 4);
+        uint64_t seq = Murmur64A(buf, 12, 0);
+        s.rng = PcgSeed(seq, MixBits(seq));
+        PcgAdvance(s.rng, uint64_t(index) * 65536ull + uint64_t(dim));
+        s.z.dimension = dim;
+        return;
+    }
+    ZSobolStart(s.z, sd, px, py, index, dim);
+}
+B2_HD float SamplerGet1D(PathSampler &s) {
+    if (s.independent) {  // rng.Uniform<Float>() (util/rng.h:120-123)
+        ++s.z.dimension;
+        return fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
+    }
+    return ZSobolGet1D(s.z);
+}
+B2_HD void SamplerGet2D(PathSampler &s, float &u0, float &u1) {
+    if (s.independent) {
+        s.z.dimension += 2;
+        u0 = fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
+        u1 = fminf(kOneMinusEps, PcgNext(s.rng) * 0x1p-32f);
+        return;
+    }
+    ZSobolGet2D(s.z, u0, u1);
 }
 
 // ------------------------------------------------------------------ pixel filter

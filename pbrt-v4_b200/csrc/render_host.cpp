@@ -283,6 +283,12 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, nOff, mi, mo, uvOff, 0};
     }
     out.rs.geomExt = (hs.hasPatches || !out.cornerAttr.empty()) ? 1u : 0u;
+    // ... or one of the less common shading features: the material variants, the independent sampler, delta lights
+    for (const MaterialDev &m : out.materials)
+        if ((m.type == MAT_DIFFUSE || m.type == MAT_DIELECTRIC) && m.params[4] != 0) out.rs.geomExt = 1u;
+    if (d->sampler_type != B200PT_SAMPLER_ZSOBOL) out.rs.geomExt = 1u;
+    for (uint32_t i = 0; i < d->n_lights; ++i)
+        if (d->lights[i].type >= B200PT_LIGHT_POINT) out.rs.geomExt = 1u;
     out.lights.resize(d->n_lights);
     for (uint32_t i = 0; i < d->n_lights; ++i) {
         const b200pt_light &l = d->lights[i];

@@ -61,9 +61,10 @@ struct LambdaIter {
     }
 };
 
-B2_HD ZSobol SamplerFor(const RenderSceneDev &rs, const PathRegs &p) {
-    ZSobol s;
-    ZSobolStart(s, rs.sampler, p.px, p.py, p.sampleIndex, p.dimension);
+template <int EXT = 1>
+B2_HD PathSampler SamplerFor(const RenderSceneDev &rs, const PathRegs &p) {
+    PathSampler s;
+    PathSamplerStart<EXT>(s, rs.sampler, p.px, p.py, p.sampleIndex, p.dimension);
     return s;
 }
 
@@ -73,17 +74,17 @@ B2_HD void GenerateCameraPath(const RenderSceneDev &rs, PathRegs &p, int px, int
     p.py = py;
     p.sampleIndex = sampleIndex;
     p.dimension = 0;
-    ZSobol s = SamplerFor(rs, p);
-    p.lambdaU = ZSobolGet1D(s);
+    PathSampler s = SamplerFor<1>(rs, p);
+    p.lambdaU = SamplerGet1D(s);
     float f0, f1;
-    ZSobolGet2D(s, f0, f1);  // GetPixel2D -> filter.Sample
+    SamplerGet2D(s, f0, f1);  // GetPixel2D -> filter.Sample
     float fx, fy;
     SampleFilter(rs.film, f0, f1, fx, fy, p.filterWeight);
     float pFilmX = px + fx + 0.5f, pFilmY = py + fy + 0.5f;
-    (void)ZSobolGet1D(s);  // time
+    (void)SamplerGet1D(s);  // time
     float l0, l1;
-    ZSobolGet2D(s, l0, l1);
-    p.dimension = s.dimension;
+    SamplerGet2D(s, l0, l1);
+    p.dimension = s.z.dimension;
     p.cameraWeight = 1.f;
     if (rs.camera.type >= 1)  // realistic, omni
         p.cameraWeight = GenerateRealisticRay(rs.camera, rs.film, pFilmX, pFilmY, l0, l1, p.rayO, p.rayD);
@@ -111,7 +112,9 @@ B2_HD void KillPath(PathRegs &p) {
 // Material::GetBxDF for the surface (materials.h: Diffuse 430-476, Conductor 491-509, Dielectric 183-203)
 // MAT >= 0: the caller knows the material type (a material-sorted queue); the constant lets the
 // compiler drop the other models from that kernel.
-template <int MAT>
+// EXT = 0: a scene without the less common features (RenderSceneDev::geomExt) - here the material variants
+// (ThinDielectric, DiffuseTransmission) - whose branches the plain kernels then do not carry.
+template <int MAT, int EXT = 1>
 B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lambda0, PathRegs &p) {
     Bsdf b;
     b.type = MAT >= 0 ? uint32_t(MAT) : mat.type;
@@ -149,12 +152,12 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
         if (mat.params[3] == 0) p.flags |= PF_TERMINATED_SECONDARY;  // eta is not a ConstantSpectrum
         if (e == 0) e = 1;
         b.eta = e;
-        if (mat.params[4] != 0) {  // ThinDielectricMaterial (materials.h:215-262): no roughness
+        if (EXT && mat.params[4] != 0) {  // ThinDielectricMaterial (materials.h:215-262): no roughness
             b.thin = 1;
             b.tr = TRDist{0, 0};
         }
     }
-    if (b.type == MAT_DIFFUSE && mat.params[4] != 0) {  // DiffuseTransmissionMaterial::GetBxDF (materials.h:891-897)
+    if (EXT && b.type == MAT_DIFFUSE && mat.params[4] != 0) {  // DiffuseTransmissionMaterial::GetBxDF (materials.h:891-897)
         b.trans = 1;
         b.specB = mat.spectrum[1];
         b.dscale = mat.params[5];
@@ -198,14 +201,16 @@ B2_HD BsdfSample EvalSample(const Bsdf &b, V3 wo, float uc, float u0, float u1, 
 }
 
 // f_k: the per-wavelength factor applied to the scalar evaluation `e` (see BsdfEval)
-B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval &e, float lam) {
+// Rk: the vertex's cached Clamp(R(lambda_k), 0, 1) of a diffuse / coated diffuse surface (ShadeVertex fills IO::SetR
+// once per vertex: the flags, the light sample and the BSDF sample all need the same 31 look-ups)
+B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval &e, float lam, float Rk) {
     switch (e.kind) {
     case 1: return e.scale;
-    case 2: return Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, 1) * e.scale;  // DiffuseMaterial clamps R
+    case 2: return Rk * e.scale;  // DiffuseMaterial clamps R
     case 6: return Clampf(b.dscale * SpectrumAt(rs.spectra[b.specA], lam), 0, 1) * e.scale;  // DiffuseTransmission: R
     case 7: return Clampf(b.dscale * SpectrumAt(rs.spectra[b.specB], lam), 0, 1) * e.scale;  //   T (materials.h:894-895)
     case 5: {  // coated diffuse: polynomial in R_k (render_layered.h)
-        float R = Clampf(SpectrumAt(rs.spectra[b.specA], lam), 0, 1);
+        float R = Rk;
         float v = e.poly[kLayerPoly - 1];
         for (int a = kLayerPoly - 2; a >= 0; --a) v = v * R + e.poly[a];
         return v;
@@ -397,7 +402,7 @@ B2_SPECTRAL_LOOP
         return;
     }
     const MaterialDev mat = rs.materials[mesh.material];
-    Bsdf bsdf = MakeBsdf<MAT>(rs, mat, LambdaIter(p.lambdaU).lam, p);
+    Bsdf bsdf = MakeBsdf<MAT, EXT>(rs, mat, LambdaIter(p.lambdaU).lam, p);
     // regularize first: it can turn a specular lobe glossy, which changes Flags() (cpu/integrators.cpp:714-718)
     if (rs.integrator.regularize && (p.flags & PF_ANY_NONSPECULAR)) BsdfRegularize(bsdf);
     // the film's VisibleSurface (film.cpp:197-213) at the first vertex with a BSDF (cpu/integrators.cpp:721-732): p, the
@@ -406,12 +411,18 @@ B2_SPECTRAL_LOOP
         io.VisibleSurface(Mid(si.pi), DotN(si.n, si.wo) < 0 ? -si.n : si.n, DotN(si.ns, si.wo) < 0 ? -si.ns : si.ns,
                           mesh.material, (int)hit[5]);
     uint32_t bflags = BsdfFlags(bsdf);
-    if (bsdf.type == MAT_DIFFUSE && !bsdf.trans) {  // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
+    const bool cachesR = (bsdf.type == MAT_DIFFUSE && !bsdf.trans) || bsdf.type == MAT_COATED_DIFFUSE;
+    if (cachesR) {  // R at the path's wavelengths, once (DiffuseMaterial / CoatedDiffuseMaterial::GetBxDF clamp it)
         bool anyR = false;
         LambdaIter li(p.lambdaU);
 B2_SPECTRAL_LOOP
-        for (int k = 0; k < kNLambda; ++k, li.Next()) anyR |= Clampf(SpectrumAt(rs.spectra[bsdf.specA], li.lam), 0, 1) != 0;
-        if (!anyR) bflags = 0;
+        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+            float R = Clampf(SpectrumAt(rs.spectra[bsdf.specA], li.lam), 0, 1);
+            io.SetR(k, R);
+            anyR |= R != 0;
+        }
+        // DiffuseBxDF::Flags: Unset when R is black (bxdfs.h:33-35)
+        if (bsdf.type == MAT_DIFFUSE && !anyR) bflags = 0;
     }
     // BSDF shading frame: Frame::FromXZ(Normalize(dpdus), ns) (bsdf.h:24-25)
     V3 fx = Normalize(si.dpdus), fz = si.ns, fy = Cross(fz, fx);
@@ -421,7 +432,7 @@ B2_SPECTRAL_LOOP
         KillPath(p);
         return;
     }
-    ZSobol s = SamplerFor(rs, p);
+    PathSampler s = SamplerFor<EXT>(rs, p);
 
     // ---- direct lighting (SampleLd, cpu/integrators.cpp:764-805)
     if (bflags & (BX_DIFFUSE | BX_GLOSSY)) {
@@ -437,9 +448,9 @@ B2_SPECTRAL_LOOP
         }
         // SampleLd evaluates the BSDF with intr.wo (normalised); Sample_f below gets -ray.d as it is
         V3 woLd = mk(Dot(si.wo, fx), Dot(si.wo, fy), Dot(si.wo, fz));
-        float uL = ZSobolGet1D(s);
+        float uL = SamplerGet1D(s);
         float uLight0, uLight1;
-        ZSobolGet2D(s, uLight0, uLight1);
+        SamplerGet2D(s, uLight0, uLight1);
         if (rs.nLights > 0) {
             // AliasTable::Sample (util/sampling.cpp:619-647) / UniformLightSampler (lightsamplers.h:33-53)
             int nl = (int)rs.nLights, lidx;
@@ -468,7 +479,7 @@ B2_SPECTRAL_LOOP
             }
             V3 cp = Mid(ctx.pi);
             // the delta lights (point, spot, distant): pdf 1, no MIS (cpu/integrators.cpp:798-799, 1386-1387)
-            const bool delta = lidx >= 0 && light.type >= LIGHT_POINT;
+            const bool delta = EXT && lidx >= 0 && light.type >= LIGHT_POINT;
             V3 wiDelta = mk(0, 0, 0);
             float attenDelta = 1.f;
             if (delta) SampleDeltaLight(light, rs.lightGeom + size_t(kLightGeomFloats) * lidx, cp, ss, wiDelta, attenDelta);
@@ -497,7 +508,7 @@ B2_SPECTRAL_LOOP
 B2_SPECTRAL_LOOP
                         for (int k = 0; k < kNLambda; ++k, li.Next()) {
                             float Le = light.scale * SpectrumAt(sp, li.lam) * atten;
-                            float f = BsdfSpectral(rs, bsdf, ev, li.lam) * absCos;
+                            float f = BsdfSpectral(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f) * absCos;
                             // volpath keeps beta * f_hat * L; the transmittance walk supplies T_ray and the MIS weight
                             io.SetLd(k, vol ? io.Beta(k) * f * Le : io.Beta(k) * (w_l * Le * f / p_l));
                             anyL |= Le != 0;
@@ -525,10 +536,10 @@ B2_SPECTRAL_LOOP
     }
 
     // ---- sample the BSDF for the next direction (cpu/integrators.cpp:728-745, BSDF::Sample_f bsdf.h:58-80)
-    float uc = ZSobolGet1D(s);
+    float uc = SamplerGet1D(s);
     float u0, u1;
-    ZSobolGet2D(s, u0, u1);
-    p.dimension = s.dimension;
+    SamplerGet2D(s, u0, u1);
+    p.dimension = s.z.dimension;
     if (woL.z == 0 || !(bflags & (BX_REFLECTION | BX_TRANSMISSION))) {
         KillPath(p);
         return;
@@ -542,7 +553,7 @@ B2_SPECTRAL_LOOP
     V3 wi = bs.wi.x * fx + bs.wi.y * fy + bs.wi.z * fz;  // Frame::FromLocal
     float absCos = AbsDotN(si.ns, wi);
 #ifdef B2_PATH_DEBUG
-    printf("      sample: f0 %.9g absdot %.9g pdf %.9g eta %.9g woL %.9g %.9g %.9g\n", BsdfSpectral(rs, bsdf, ev, 500.f),
+    printf("      sample: f0 %.9g absdot %.9g pdf %.9g eta %.9g woL %.9g %.9g %.9g\n", BsdfSpectral(rs, bsdf, ev, 500.f, 0.f),
            absCos, bs.pdf, bs.eta, woL.x, woL.y, woL.z);
 #endif
     bool anyF = false;
@@ -550,7 +561,7 @@ B2_SPECTRAL_LOOP
         LambdaIter li(p.lambdaU);
 B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k, li.Next()) {
-            float f = BsdfSpectral(rs, bsdf, ev, li.lam);
+            float f = BsdfSpectral(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f);
             anyF |= f != 0;
             io.SetBeta(k, io.Beta(k) * (f * absCos / bs.pdf));
         }
@@ -581,9 +592,9 @@ B2_SPECTRAL_LOOP
         const float avg = AvgRu(io);
         float mc = io.Beta(0) * p.etaScale / avg;
         for (int k = 1; k < kNLambda; ++k) mc = fmaxf(mc, io.Beta(k) * p.etaScale / avg);
-        s = SamplerFor(rs, p);
-        float uRR = ZSobolGet1D(s);
-        p.dimension = s.dimension;
+        s = SamplerFor<EXT>(rs, p);
+        float uRR = SamplerGet1D(s);
+        p.dimension = s.z.dimension;
         if (mc < 1 && p.depth > 1) {
             float q = fmaxf(0.f, 1 - mc);
             if (uRR < q) {
@@ -602,9 +613,9 @@ B2_SPECTRAL_LOOP
 #endif
     if (maxComp < 1 && p.depth > 1) {
         float q = fmaxf(0.f, 1 - maxComp);
-        s = SamplerFor(rs, p);
-        float ur = ZSobolGet1D(s);
-        p.dimension = s.dimension;
+        s = SamplerFor<EXT>(rs, p);
+        float ur = SamplerGet1D(s);
+        p.dimension = s.z.dimension;
         if (ur < q) {
             KillPath(p);
             return;

@@ -151,7 +151,9 @@ struct RenderSceneDev {
     float lightBvhBounds[6];
     const MediumDev *media;
     uint32_t nMedia;
-    uint32_t geomExt;         // some mesh is a bilinear patch mesh or has per-corner attributes (else the EXT = 0 kernels run)
+    uint32_t geomExt;         // some mesh is a bilinear patch mesh or has per-corner attributes, or the scene uses a material
+                              // variant (thin dielectric, diffuse transmission), the independent sampler or a delta light:
+                              // the EXT = 1 kernels run; else the EXT = 0 ones, which carry none of those branches
     const float *cornerAttr;  // per-corner normals / uv of the meshes that have them (MeshAttrDev::nOff, uvOff)
     const float *lightGeom;   // delta lights' placement (kLightGeomFloats per light, all lights), or null when there are none
     const int32_t *materialIds;  // GBufferFilm: the host's Material::materialId per material (materials.cpp:738), or null

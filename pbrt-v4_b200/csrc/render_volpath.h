@@ -67,7 +67,7 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
     }
     if (lp.lidx < 0) return lp;
     const LightDev &light = rs.lights[lp.lidx];
-    if (light.type >= LIGHT_POINT) {  // point, spot, distant
+    if (EXT && light.type >= LIGHT_POINT) {  // point, spot, distant
         lp.delta = true;
         lp.ok = SampleDeltaLight(light, rs.lightGeom + size_t(kLightGeomFloats) * lp.lidx, Mid(ctx.pi), lp.ss, lp.wi, lp.atten);
         return lp;
@@ -114,12 +114,12 @@ struct VolMediumState {
 
 B2_HD void VolMediumBegin(const RenderSceneDev &rs, PathRegs &p, float tHit, VolMediumState &st) {
     const MediumDev &m = rs.media[p.medium];
-    ZSobol s = SamplerFor(rs, p);
-    uint64_t hash0 = Hash1f(ZSobolGet1D(s));
-    uint64_t hash1 = Hash1f(ZSobolGet1D(s));
+    PathSampler s = SamplerFor<1>(rs, p);
+    uint64_t hash0 = Hash1f(SamplerGet1D(s));
+    uint64_t hash1 = Hash1f(SamplerGet1D(s));
     st.rng = PcgSeed(hash0, hash1);
-    float u = ZSobolGet1D(s);
-    p.dimension = s.dimension;
+    float u = SamplerGet1D(s);
+    p.dimension = s.z.dimension;
     MediumSpectra(rs, m, p.lambdaU, st.sigA, st.sigS, st.sigT);
     st.terminated = st.scattered = false;
     st.pScatter = mk(0, 0, 0);
@@ -145,12 +145,12 @@ B2_HD int VolMediumEnd(const RenderSceneDev &rs, PathRegs &p, VolMediumState &st
 // the fast split walk of the persistent kernel (TMajFastWalk): st.walk is not used, `fw` is
 B2_HD void VolMediumBeginFast(const RenderSceneDev &rs, PathRegs &p, float tHit, VolMediumState &st, TMajFastWalk &fw) {
     const MediumDev &m = rs.media[p.medium];
-    ZSobol s = SamplerFor(rs, p);
-    uint64_t hash0 = Hash1f(ZSobolGet1D(s));
-    uint64_t hash1 = Hash1f(ZSobolGet1D(s));
+    PathSampler s = SamplerFor<1>(rs, p);
+    uint64_t hash0 = Hash1f(SamplerGet1D(s));
+    uint64_t hash1 = Hash1f(SamplerGet1D(s));
     st.rng = PcgSeed(hash0, hash1);
-    float u = ZSobolGet1D(s);
-    p.dimension = s.dimension;
+    float u = SamplerGet1D(s);
+    p.dimension = s.z.dimension;
     MediumSpectra(rs, m, p.lambdaU, st.sigA, st.sigS, st.sigT);
     st.terminated = st.scattered = false;
     st.pScatter = mk(0, 0, 0);
@@ -206,10 +206,10 @@ B2_SPECTRAL_LOOP
     LightCtx ctx;
     ctx.pi = MakeP3i(pS, mk(0, 0, 0));
     ctx.n = ctx.ns = mk(0, 0, 0);
-    ZSobol s = SamplerFor(rs, p);
-    float uL = ZSobolGet1D(s);
+    PathSampler s = SamplerFor<EXT>(rs, p);
+    float uL = SamplerGet1D(s);
     float uLight0, uLight1;
-    ZSobolGet2D(s, uLight0, uLight1);
+    SamplerGet2D(s, uLight0, uLight1);
     LightPick lp = PickAndSampleLight<LBVH, EXT>(rs, ctx, uL, uLight0, uLight1);
     if (lp.ok) {
         float fHat = HenyeyGreenstein(Dot(woN, lp.wi), m.g);
@@ -237,8 +237,8 @@ B2_SPECTRAL_LOOP
         }
     }
     float u0, u1;
-    ZSobolGet2D(s, u0, u1);
-    p.dimension = s.dimension;
+    SamplerGet2D(s, u0, u1);
+    p.dimension = s.z.dimension;
     float pdf;
     V3 wi = SampleHenyeyGreenstein(-p.rayD, m.g, u0, u1, &pdf);
     if (pdf == 0) return VOL_TERMINATED;

@@ -48,6 +48,9 @@ struct HostIO {
     float shTMax;
     float Beta(int k) const { return beta[k]; }
     void SetBeta(int k, float v) { beta[k] = v; }
+    float refl[kNLambda];  // the vertex's cached reflectance
+    float R(int k) const { return refl[k]; }
+    void SetR(int k, float v) { refl[k] = v; }
     void VisibleSurface(V3, V3, V3, int, int) {}
     void AddL(int k, float v) { L[k] += v; }
     void ShadowBegin() {}
