@@ -216,9 +216,14 @@ typedef struct b200pt_material {
     int32_t spectrum[4]; /* diffuse: [0] reflectance (materials.h:430-476); with params[4] != 0 the material is a
                           * DiffuseTransmissionMaterial (materials.h:869-927, DiffuseTransmissionBxDF bxdfs.h:218-297):
                           * [0] reflectance, [1] transmittance, params[5] = scale */
-    float params[8];     /* dielectric: {uRoughness, vRoughness, remapRoughness, eta is a ConstantSpectrum, THIN};
+    float params[12];    /* dielectric: {uRoughness, vRoughness, remapRoughness, eta is a ConstantSpectrum, THIN};
                           * THIN != 0 = ThinDielectricMaterial (materials.h:215-262, ThinDielectricBxDF bxdfs.h:342-410):
-                          * specular reflection + straight-through transmission, the roughness entries are ignored */
+                          * specular reflection + straight-through transmission, the roughness entries are ignored.
+                          * coated diffuse: {interface uRoughness, vRoughness, remapRoughness, eta is a ConstantSpectrum,
+                          * thickness, g, maxdepth, nsamples, COATED_CONDUCTOR, conductor uRoughness, vRoughness};
+                          * spectrum = {reflectance, albedo (black), interface eta}.  COATED_CONDUCTOR != 0 =
+                          * CoatedConductorMaterial (materials.h:695-790, materials.cpp:392-438; LayeredBxDF over a
+                          * ConductorBxDF): spectrum = {conductor eta or -1, k, interface eta, reflectance when eta is -1} */
 } b200pt_material;
 
 /* DiffuseAreaLight on one triangle or one bilinear patch (lights.h:407-500; `tri` is then the patch index of a

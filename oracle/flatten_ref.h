@@ -615,10 +615,10 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         if (!ct) die("only constant float textures are dumped so far");
         return ct->value;
     };
-    // materials_i: {type, spectrum[4]}; materials_f: params[8] (layout: include/b200pt.h b200pt_material)
+    // materials_i: {type, spectrum[4]}; materials_f: params[12] (layout: include/b200pt.h b200pt_material)
     for (pbrt::Material mtl : materialList) {
         int32_t rec[5] = {-1, -1, -1, -1, -1};
-        float prm[8] = {0};
+        float prm[12] = {0};
         if (!mtl) {
             rec[0] = -1;
         } else if (const DiffuseMaterial *dm = mtl.CastOrNullptr<DiffuseMaterial>()) {
@@ -669,10 +669,32 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             prm[5] = constFloat(cd->g);
             prm[6] = float(cd->maxDepth);
             prm[7] = float(cd->nSamples);
+        } else if (const CoatedConductorMaterial *cc = mtl.CastOrNullptr<CoatedConductorMaterial>()) {
+            if (cc->displacement || cc->normalMap) die("displacement / normal maps are not dumped");
+            const SpectrumConstantTexture *alb = cc->albedo.CastOrNullptr<SpectrumConstantTexture>();
+            if (!alb) die("only constant spectrum textures are dumped so far");
+            for (int l = 395; l <= 705; ++l)
+                if (alb->value(Float(l)) != 0) die("coatedconductor with albedo != 0 (a medium between the layers) is not dumped");
+            rec[0] = 3;  // the coated queue, params[8] = conductor base
+            rec[1] = constSpec(cc->conductorEta);
+            rec[2] = constSpec(cc->k);
+            rec[3] = pool.add(cc->interfaceEta, 1);
+            rec[4] = constSpec(cc->reflectance);
+            prm[0] = constFloat(cc->interfaceURoughness);
+            prm[1] = constFloat(cc->interfaceVRoughness);
+            prm[2] = cc->remapRoughness ? 1.f : 0.f;
+            prm[3] = cc->interfaceEta.Is<ConstantSpectrum>() ? 1.f : 0.f;
+            prm[4] = constFloat(cc->thickness);
+            prm[5] = constFloat(cc->g);
+            prm[6] = float(cc->maxDepth);
+            prm[7] = float(cc->nSamples);
+            prm[8] = 1.f;
+            prm[9] = constFloat(cc->conductorURoughness);
+            prm[10] = constFloat(cc->conductorVRoughness);
         } else
-            die("only diffuse, diffusetransmission, conductor, dielectric, thindielectric and coateddiffuse materials are dumped so far");
+            die("only diffuse, diffusetransmission, coatedconductor, conductor, dielectric, thindielectric and coateddiffuse materials are dumped so far");
         matI.insert(matI.end(), rec, rec + 5);
-        matF.insert(matF.end(), prm, prm + 8);
+        matF.insert(matF.end(), prm, prm + 12);
     }
     {  // Material::materialId (materials.cpp:738), GBufferFilm's MaterialId channel
         std::vector<int32_t> ids;
@@ -680,7 +702,7 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         w.i32("material_ids", {uint32_t(ids.size())}, ids);
     }
     w.i32("materials_i", {uint32_t(materialList.size()), 5}, matI);
-    w.f32("materials_f", {uint32_t(materialList.size()), 8}, matF);
+    w.f32("materials_f", {uint32_t(materialList.size()), 12}, matF);
 
     // ---- lights + the power sampler's alias table (lightsamplers.cpp:76-96, util/sampling.cpp:562-617)
     PowerLightSampler pls(pstd::span<const Light>(lights.data(), lights.size()), Allocator());

@@ -219,7 +219,8 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         const int32_t *rec = mi.i() + 5 * i;
         m.materials[i].type = rec[0] >= 0 ? uint32_t(rec[0]) : 0u;
         memcpy(m.materials[i].spectrum, rec + 1, 16);
-        memcpy(m.materials[i].params, mf.f() + 8 * i, 32);
+        memset(m.materials[i].params, 0, sizeof(m.materials[i].params));
+        memcpy(m.materials[i].params, mf.f() + mf.cols() * i, 4 * std::min<size_t>(mf.cols(), 12));
     }
     const Table &li = T.at("lights_i"), &lf = T.at("lights_f");
     m.lights.resize(std::max<size_t>(1, li.rows()));

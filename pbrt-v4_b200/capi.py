@@ -138,7 +138,7 @@ class Spectrum(C.Structure):
 
 
 class Material(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("spectrum", C.c_int32 * 4), ("params", C.c_float * 8)]
+    _fields_ = [("type", C.c_uint32), ("spectrum", C.c_int32 * 4), ("params", C.c_float * 12)]
 
 
 class Light(C.Structure):

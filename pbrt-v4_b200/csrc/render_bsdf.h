@@ -163,6 +163,7 @@ struct BsdfSample {
 // 3 conductor ((D*F_k)*G)/denom with F_k = FrComplex(cosF, eta_k, k_k), 4 specular conductor F_k/denom.
 // 5 coated diffuse: sum_a poly[a] * R_k^a (the random walk of LayeredBxDF only ever multiplies the
 // throughput by scalars and by the diffuse base's R_k, so its value is a polynomial in R_k).
+// 8 coated conductor: the value at each wavelength is in the caller's array of kNLambda floats (render_layered.h).
 // 6 / 7 diffuse transmission: clamp(dscale*R_k)*scale on wo's side, clamp(dscale*T_k)*scale on the other.
 constexpr int kLayerPoly = 14;
 struct BsdfEval {
@@ -187,6 +188,10 @@ struct Bsdf {
     float thickness, rMax;  // rMax = max_k R_k at this path's wavelengths
     int maxDepth, nSamples;
     int32_t layerSeed;      // Options::seed, hashed into the random walks' generators
+    // coated conductor (LayeredBxDF<DielectricBxDF, ConductorBxDF, true>): the base's microfacet distribution; its eta /
+    // k (or reflectance) are specA / specB as for a conductor, the coating's index is `eta`
+    uint32_t coatCond;
+    TRDist condTr;
 };
 
 // ---- DielectricBxDF with explicit TransportMode and BxDFReflTransFlags (bxdfs.cpp:77-255): the coated
@@ -309,6 +314,7 @@ B2_HD uint32_t BsdfFlags(const Bsdf &b) {
         uint32_t f = BX_REFLECTION;
         bool topSpecular = TRSmooth(b.tr);
         if (topSpecular) f |= BX_SPECULAR;
+        if (b.coatCond) return f | ((!topSpecular || !TRSmooth(b.condTr)) ? BX_GLOSSY : 0u);  // conductor bottom
         if (b.rMax != 0) f |= BX_DIFFUSE;
         else if (!topSpecular) f |= BX_GLOSSY;
         return f;
@@ -319,6 +325,7 @@ B2_HD uint32_t BsdfFlags(const Bsdf &b) {
 B2_HD void BsdfRegularize(Bsdf &b) {
     if (b.type == MAT_DIELECTRIC && b.thin) return;  // ThinDielectricBxDF::Regularize does nothing (bxdfs.h:400-401)
     if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC || b.type == MAT_COATED_DIFFUSE) TRRegularize(b.tr);
+    if (b.type == MAT_COATED_DIFFUSE && b.coatCond) TRRegularize(b.condTr);  // LayeredBxDF::Regularize: top and bottom
 }
 
 B2_HD BsdfEval ZeroEval() {

@@ -247,6 +247,16 @@ B2_HD float SpectrumAt(const SpectrumTable &t, float lambda) {
     return Lerp(x - i, t.values[i], t.values[i + 1]);
 }
 
+// lambda_k of SampledWavelengths::SampleUniform (util/spectrum.h:318-336), one at a time
+struct LambdaIter {
+    float lam;
+    B2_HD explicit LambdaIter(float u) : lam(Lerp(u, kLambdaMin, kLambdaMax)) {}
+    B2_HD void Next() {
+        lam = lam + (kLambdaMax - kLambdaMin) / kNLambda;
+        if (lam > kLambdaMax) lam = kLambdaMin + (lam - kLambdaMax);
+    }
+};
+
 // ------------------------------------------------------------------ camera (cameras.cpp:433-456)
 B2_HD V3 XformPoint(const float *m, V3 p) {  // Transform::operator()(Point3) util/transform.h
     float x = m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3];

@@ -227,6 +227,15 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("conductor needs eta and k, or reflectance");
             break;
         case B200PT_MAT_COATED_DIFFUSE: {  // reflectance, albedo (must be black: no medium between the layers), eta
+            if (m.params[8] != 0) {  // coated conductor: {conductor eta | -1, k, interface eta, reflectance}; albedo is not handed over
+                if (!opt(m.spectrum[0]) || !opt(m.spectrum[1]) || !specOk(m.spectrum[2]) || !opt(m.spectrum[3]))
+                    return bad("material spectrum index out of range");
+                if (m.spectrum[0] >= 0 ? m.spectrum[1] < 0 : m.spectrum[3] < 0)
+                    return bad("coatedconductor needs conductor eta and k, or reflectance");
+                if (m.params[6] < 1 || m.params[6] > 24 || m.params[7] < 1)
+                    return bad("coatedconductor maxdepth must be 1..24 and nsamples >= 1");
+                break;
+            }
             if (!specOk(m.spectrum[0]) || !specOk(m.spectrum[2]) || !opt(m.spectrum[1]))
                 return bad("material spectrum index out of range");
             if (m.spectrum[1] >= 0)
@@ -242,7 +251,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         }
         out.materials[i].type = m.type;
         std::memcpy(out.materials[i].spectrum, m.spectrum, 16);
-        std::memcpy(out.materials[i].params, m.params, 32);
+        std::memcpy(out.materials[i].params, m.params, sizeof(m.params));
     }
     // (mesh, tri) -> primitive slot of the geometry scene
     std::map<uint64_t, uint32_t> slotOf;
@@ -285,7 +294,8 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     out.rs.geomExt = (hs.hasPatches || !out.cornerAttr.empty()) ? 1u : 0u;
     // ... or one of the less common shading features: the material variants, the independent sampler, delta lights
     for (const MaterialDev &m : out.materials)
-        if ((m.type == MAT_DIFFUSE || m.type == MAT_DIELECTRIC) && m.params[4] != 0) out.rs.geomExt = 1u;
+        if (((m.type == MAT_DIFFUSE || m.type == MAT_DIELECTRIC) && m.params[4] != 0) || (m.type == MAT_COATED_DIFFUSE && m.params[8] != 0))
+            out.rs.geomExt = 1u;
     if (d->sampler_type != B200PT_SAMPLER_ZSOBOL) out.rs.geomExt = 1u;
     for (uint32_t i = 0; i < d->n_lights; ++i)
         if (d->lights[i].type >= B200PT_LIGHT_POINT) out.rs.geomExt = 1u;

@@ -51,16 +51,6 @@ struct PathRegs {
     float rayTMax;
 };
 
-// lambda_k of SampledWavelengths::SampleUniform (util/spectrum.h:318-336), one at a time
-struct LambdaIter {
-    float lam;
-    B2_HD explicit LambdaIter(float u) : lam(Lerp(u, kLambdaMin, kLambdaMax)) {}
-    B2_HD void Next() {
-        lam = lam + (kLambdaMax - kLambdaMin) / kNLambda;
-        if (lam > kLambdaMax) lam = kLambdaMin + (lam - kLambdaMax);
-    }
-};
-
 template <int EXT = 1>
 B2_HD PathSampler SamplerFor(const RenderSceneDev &rs, const PathRegs &p) {
     PathSampler s;
@@ -130,6 +120,8 @@ B2_HD Bsdf MakeBsdf(const RenderSceneDev &rs, const MaterialDev &mat, float lamb
     b.rMax = 0;
     b.maxDepth = b.nSamples = 0;
     b.layerSeed = 0;  // Options::seed (options.h), 0 unless the host was started with --seed
+    b.coatCond = 0;
+    b.condTr = TRDist{0, 0};
     if (b.type == MAT_CONDUCTOR || b.type == MAT_DIELECTRIC || b.type == MAT_COATED_DIFFUSE) {
         float ur = mat.params[0], vr = mat.params[1];
         if (mat.params[2] != 0) {  // remaproughness: RoughnessToAlpha = sqrt
@@ -179,6 +171,23 @@ B2_SPECTRAL_LOOP
         b.thickness = fmaxf(mat.params[4], 1.17549435e-38f);
         b.maxDepth = (int)mat.params[6];
         b.nSamples = (int)mat.params[7];
+        if (EXT && mat.params[8] != 0) {  // CoatedConductorMaterial::GetBxDF (materials.cpp:392-438)
+            b.coatCond = 1;
+            float cu = mat.params[9], cv = mat.params[10];
+            if (mat.params[2] != 0) {
+                cu = sqrtf(cu);
+                cv = sqrtf(cv);
+            }
+            b.condTr = MakeTR(cu, cv);
+            if (mat.spectrum[0] >= 0) {
+                b.specA = mat.spectrum[0];
+                b.specB = mat.spectrum[1];
+            } else {
+                b.specA = mat.spectrum[3];  // reflectance; k derived per wavelength
+                b.specB = -1;
+            }
+            return b;
+        }
         float rm = 0;
         LambdaIter li(p.lambdaU);
 B2_SPECTRAL_LOOP
@@ -189,13 +198,19 @@ B2_SPECTRAL_LOOP
 }
 
 // the four BxDF entry points with the layered model added (it needs its own header)
-B2_HD BsdfEval EvalF(const Bsdf &b, V3 wo, V3 wi) {
+// (rs, lambdaU: the coated conductor's walks need the base's spectra at the path's wavelengths)
+// spec: kNLambda floats for its per-wavelength value (BsdfEval kind 8)
+B2_HD BsdfEval EvalF(const RenderSceneDev &rs, float lambdaU, const Bsdf &b, V3 wo, V3 wi, float *spec) {
+    if (b.type == MAT_COATED_DIFFUSE && b.coatCond) return CoatedCondF(rs, b, lambdaU, wo, wi, b.layerSeed, spec);
     return b.type == MAT_COATED_DIFFUSE ? CoatedF(b, wo, wi, b.layerSeed) : BsdfF(b, wo, wi);
 }
 B2_HD float EvalPDF(const Bsdf &b, V3 wo, V3 wi) {
+    if (b.type == MAT_COATED_DIFFUSE && b.coatCond) return CoatedCondPDF(b, wo, wi, b.layerSeed);
     return b.type == MAT_COATED_DIFFUSE ? CoatedPDF(b, wo, wi, b.layerSeed) : BsdfPDF(b, wo, wi);
 }
-B2_HD BsdfSample EvalSample(const Bsdf &b, V3 wo, float uc, float u0, float u1, BsdfEval &ev) {
+B2_HD BsdfSample EvalSample(const RenderSceneDev &rs, float lambdaU, const Bsdf &b, V3 wo, float uc, float u0, float u1,
+                            BsdfEval &ev, float *spec) {
+    if (b.type == MAT_COATED_DIFFUSE && b.coatCond) return CoatedCondSample(rs, b, lambdaU, wo, uc, u0, u1, b.layerSeed, ev, spec);
     return b.type == MAT_COATED_DIFFUSE ? CoatedSample(b, wo, uc, u0, u1, b.layerSeed, ev)
                                         : BsdfSampleF(b, wo, uc, u0, u1, ev);
 }
@@ -203,7 +218,9 @@ B2_HD BsdfSample EvalSample(const Bsdf &b, V3 wo, float uc, float u0, float u1, 
 // f_k: the per-wavelength factor applied to the scalar evaluation `e` (see BsdfEval)
 // Rk: the vertex's cached Clamp(R(lambda_k), 0, 1) of a diffuse / coated diffuse surface (ShadeVertex fills IO::SetR
 // once per vertex: the flags, the light sample and the BSDF sample all need the same 31 look-ups)
-B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval &e, float lam, float Rk) {
+template <int EXT = 1>
+B2_HD float BsdfSpectral(const RenderSceneDev &rs, const Bsdf &b, const BsdfEval &e, float lam, float Rk, int k, const float *spec) {
+    if (EXT && e.kind == 8) return spec[k];  // coated conductor: the walk's value at wavelength k (EXT = 1 kernels only)
     switch (e.kind) {
     case 1: return e.scale;
     case 2: return Rk * e.scale;  // DiffuseMaterial clamps R
@@ -411,7 +428,8 @@ B2_SPECTRAL_LOOP
         io.VisibleSurface(Mid(si.pi), DotN(si.n, si.wo) < 0 ? -si.n : si.n, DotN(si.ns, si.wo) < 0 ? -si.ns : si.ns,
                           mesh.material, (int)hit[5]);
     uint32_t bflags = BsdfFlags(bsdf);
-    const bool cachesR = (bsdf.type == MAT_DIFFUSE && !bsdf.trans) || bsdf.type == MAT_COATED_DIFFUSE;
+    float spec8[EXT ? kNLambda : 1];  // a coated conductor's value per wavelength (BsdfEval kind 8)
+    const bool cachesR = (bsdf.type == MAT_DIFFUSE && !bsdf.trans) || (bsdf.type == MAT_COATED_DIFFUSE && !bsdf.coatCond);
     if (cachesR) {  // R at the path's wavelengths, once (DiffuseMaterial / CoatedDiffuseMaterial::GetBxDF clamp it)
         bool anyR = false;
         LambdaIter li(p.lambdaU);
@@ -494,7 +512,7 @@ B2_SPECTRAL_LOOP
                         atten = fmaxf((1.0f - (light.tanFalloffEnd * tan_a)) * light.normalizeFalloffEnd, 0.0f);
                     }
                     V3 wiL = mk(Dot(wi, fx), Dot(wi, fy), Dot(wi, fz));
-                    BsdfEval ev = (woLd.z == 0) ? ZeroEval() : EvalF(bsdf, woLd, wiL);  // BSDF::f (bsdf.h:37-43)
+                    BsdfEval ev = (woLd.z == 0) ? ZeroEval() : EvalF(rs, p.lambdaU, bsdf, woLd, wiL, spec8);  // BSDF::f (bsdf.h:37-43)
                     if (ev.kind != 0) {
                         float absCos = AbsDotN(si.ns, wi);
                         float p_l = pmf * ss.pdf;
@@ -508,7 +526,7 @@ B2_SPECTRAL_LOOP
 B2_SPECTRAL_LOOP
                         for (int k = 0; k < kNLambda; ++k, li.Next()) {
                             float Le = light.scale * SpectrumAt(sp, li.lam) * atten;
-                            float f = BsdfSpectral(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f) * absCos;
+                            float f = BsdfSpectral<EXT>(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f, k, spec8) * absCos;
                             // volpath keeps beta * f_hat * L; the transmittance walk supplies T_ray and the MIS weight
                             io.SetLd(k, vol ? io.Beta(k) * f * Le : io.Beta(k) * (w_l * Le * f / p_l));
                             anyL |= Le != 0;
@@ -545,7 +563,7 @@ B2_SPECTRAL_LOOP
         return;
     }
     BsdfEval ev;
-    BsdfSample bs = EvalSample(bsdf, woL, uc, u0, u1, ev);
+    BsdfSample bs = EvalSample(rs, p.lambdaU, bsdf, woL, uc, u0, u1, ev, spec8);
     if (!bs.ok || bs.pdf == 0 || bs.wi.z == 0) {
         KillPath(p);
         return;
@@ -553,7 +571,7 @@ B2_SPECTRAL_LOOP
     V3 wi = bs.wi.x * fx + bs.wi.y * fy + bs.wi.z * fz;  // Frame::FromLocal
     float absCos = AbsDotN(si.ns, wi);
 #ifdef B2_PATH_DEBUG
-    printf("      sample: f0 %.9g absdot %.9g pdf %.9g eta %.9g woL %.9g %.9g %.9g\n", BsdfSpectral(rs, bsdf, ev, 500.f, 0.f),
+    printf("      sample: f0 %.9g absdot %.9g pdf %.9g eta %.9g woL %.9g %.9g %.9g\n", BsdfSpectral<EXT>(rs, bsdf, ev, 500.f, 0.f, 0, spec8),
            absCos, bs.pdf, bs.eta, woL.x, woL.y, woL.z);
 #endif
     bool anyF = false;
@@ -561,7 +579,7 @@ B2_SPECTRAL_LOOP
         LambdaIter li(p.lambdaU);
 B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k, li.Next()) {
-            float f = BsdfSpectral(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f);
+            float f = BsdfSpectral<EXT>(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f, k, spec8);
             anyF |= f != 0;
             io.SetBeta(k, io.Beta(k) * (f * absCos / bs.pdf));
         }

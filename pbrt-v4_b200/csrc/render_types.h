@@ -28,7 +28,7 @@ enum MaterialType : uint32_t { MAT_DIFFUSE = 0, MAT_CONDUCTOR = 1, MAT_DIELECTRI
 struct MaterialDev {
     uint32_t type;
     int32_t spectrum[4];  // diffuse: [0] reflectance
-    float params[8];
+    float params[12];     // layout per material: include/b200pt.h b200pt_material
 };
 
 // DiffuseAreaLight on one triangle (lights.h:410-470) + its alias-table bin (util/sampling.h:804).

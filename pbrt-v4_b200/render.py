@@ -129,7 +129,8 @@ class RenderScene:
             mi = d["materials_i"][i]
             mats[i].type = int(mi[0]) if mi[0] >= 0 else 0
             mats[i].spectrum[:] = [int(x) for x in mi[1:5]]
-            mats[i].params[:] = [float(x) for x in d["materials_f"][i]]
+            mf = [float(x) for x in d["materials_f"][i]]  # 8 columns in dumps older than the coated conductor, 12 since
+            mats[i].params[:] = mf + [0.0] * (12 - len(mf))
         lights = (capi.Light * max(nl, 1))()
         for i in range(nl):
             li, lf = d["lights_i"][i], d["lights_f"][i]

@@ -356,6 +356,15 @@ MATERIALS = {
     "thin_dielectric_glass": 'Material "thindielectric" "spectrum eta" "glass-BK7"',
     "diffuse_transmission": 'Material "diffusetransmission" "rgb reflectance" [0.3 0.5 0.2] "rgb transmittance" [0.5 0.4 0.2]',
     "diffuse_transmission_scaled": 'Material "diffusetransmission" "rgb reflectance" [0.1 0.1 0.1] "rgb transmittance" [0.3 0.45 0.6] "float scale" 1.8',
+    # CoatedConductorMaterial (materials.h:695-790): a clear coat over copper (rough base under a smooth coat), and a
+    # rough coat over a mirror-like base given by its reflectance
+    "coated_conductor": 'Material "coatedconductor" "spectrum conductor.eta" "metal-Cu-eta" "spectrum conductor.k" "metal-Cu-k" '
+                        '"float conductor.roughness" 0.15 "float interface.roughness" 0',
+    "coated_conductor_rough": 'Material "coatedconductor" "rgb reflectance" [0.9 0.7 0.4] "float conductor.roughness" 0 '
+                              '"float interface.roughness" 0.1 "float thickness" 0.02',
+    "coated_conductor_both": 'Material "coatedconductor" "spectrum conductor.eta" "metal-Au-eta" "spectrum conductor.k" "metal-Au-k" '
+                             '"float conductor.uroughness" 0.2 "float conductor.vroughness" 0.08 "float interface.roughness" 0.05 '
+                             '"spectrum interface.eta" "glass-BK7"',
     "coated_diffuse": 'Material "coateddiffuse" "rgb reflectance" [0.2 0.3 0.7] "float roughness" 0',
     "coated_diffuse_rough": 'Material "coateddiffuse" "rgb reflectance" [0.7 0.3 0.2] "float roughness" 0.1 "float thickness" 0.02',
 }

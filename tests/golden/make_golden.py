@@ -223,6 +223,11 @@ TIGHT_CASES = {
     "tight_gaussian": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter="gaussian")),
     "tight_mitchell": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter='"mitchell" "float B" 0.2 "float C" 0.4')),
     "tight_sinc": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter='"sinc" "float xradius" 3 "float yradius" 2.5')),
+    # CoatedConductorMaterial: smooth coat over rough copper + rough coat over a smooth base; and both rough
+    # with a dispersive coat (TerminateSecondary)
+    "tight_coatcond": ("cornell", dict(res=32, spp=2048, maxdepth=5, boxes=("coated_conductor", "coated_conductor_rough"))),
+    "tight_coatcond2": ("cornell", dict(res=32, spp=4096, maxdepth=5, boxes=("coated_conductor_both", "coated_conductor"),
+                                        regularize=True)),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),
 }
