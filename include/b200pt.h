@@ -233,8 +233,10 @@ typedef struct b200pt_material {
 /* B200PT_LIGHT_POINT / SPOT / DISTANT: PointLight (lights.h:189-239), SpotLight (lights.h:747-801), DistantLight
  * (lights.h:242-297) - `spectrum` is I / Lemit, `scale` the light's scale; mesh / tri and the falloff fields are
  * unused, the placement comes from b200pt_render_desc::light_geometry. */
+/* B200PT_LIGHT_IMAGE_INFINITE: ImageInfiniteLight (lights.h:557-643) - `spectrum` is the image colour space's illuminant,
+ * `scale` the light's scale; image and sampling distribution come through b200pt_render_desc::env_*; one per scene. */
 enum { B200PT_LIGHT_AREA_TRIANGLE = 0, B200PT_LIGHT_UNIFORM_INFINITE = 1, B200PT_LIGHT_POINT = 2, B200PT_LIGHT_SPOT = 3,
-       B200PT_LIGHT_DISTANT = 4 };
+       B200PT_LIGHT_DISTANT = 4, B200PT_LIGHT_IMAGE_INFINITE = 5 };
 typedef struct b200pt_light {
     uint32_t mesh, tri;
     int32_t spectrum; /* Lemit */
@@ -388,12 +390,23 @@ typedef struct b200pt_render_desc {
      * other light types are ignored); NULL when the scene has none.  Row: [0..2] point / spot: renderFromLight(0,0,0)
      * (lights.h:224, 787); distant: Normalize(renderFromLight(0,0,1)) (lights.h:285); [3] distant: sceneRadius
      * (DistantLight::Preprocess, lights.h:277-279); [4..12] spot: upper 3 x 3 of renderFromLight's inverse, row major
-     * (lights.h:790); [13] spot cosFalloffStart, [14] spot cosFalloffEnd (lights.cpp:1376-1385); [15] 0. */
+     * (lights.h:790); [13] spot cosFalloffStart, [14] spot cosFalloffEnd (lights.cpp:1376-1385).
+     * Image infinite light: [0..8] upper 3 x 3 of renderFromLight, [9..17] of its inverse (both row major), [18]
+     * sceneRadius (ImageInfiniteLight::Preprocess). */
     const float *light_geometry;
     const float *filter_table; /* see filter_type; NULL for the box filter */
     int32_t filter_table_size[2];
+    /* the B200PT_LIGHT_IMAGE_INFINITE light's equal-area square image, env_resolution pixels a side, row-major:
+     * env_image = per pixel the RGBIlluminantSpectrum of its (clamped) RGB - {c0, c1, c2} of the RGBSigmoidPolynomial
+     * and the spectrum's scale (util/spectrum.cpp RGBIlluminantSpectrum, util/color.h) - so the library needs no
+     * RGB-to-spectrum table; env_distribution = the function of the light's compensatedDistribution
+     * (lights.cpp:1064-1070: max(luminance - average, 0), or 1 everywhere), from which the library builds the
+     * PiecewiseConstant2D as the reference does.  NULL / 0 without such a light. */
+    const float *env_image;
+    const float *env_distribution;
+    int32_t env_resolution;
 } b200pt_render_desc;
-#define B200PT_LIGHT_GEOMETRY_FLOATS 16
+#define B200PT_LIGHT_GEOMETRY_FLOATS 24
 enum { B200PT_SAMPLER_ZSOBOL = 0, B200PT_SAMPLER_INDEPENDENT = 1 };
 enum { B200PT_FILTER_BOX = 0, B200PT_FILTER_GAUSSIAN = 1, B200PT_FILTER_MITCHELL = 2, B200PT_FILTER_SINC = 3, B200PT_FILTER_TRIANGLE = 4 };
 

@@ -718,31 +718,58 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             continue;
         }
         // the delta lights: placement in lights_geom (include/b200pt.h b200pt_render_desc::light_geometry)
-        auto deltaLight = [&](int type, const DenselySampledSpectrum *spec, float scale, const float (&g)[16]) {
+        auto deltaLight = [&](int type, const DenselySampledSpectrum *spec, float scale, const float (&g)[24]) {
             if (!lemitId.count(spec)) lemitId[spec] = pool.add(spec, 0);
             lightI.insert(lightI.end(), {-1, -1, lemitId[spec], 0, bin.alias, -1, type});
             lightF.insert(lightF.end(), {scale, 0.f, 0.f, 0.f, bin.q, bin.p});
-            if (lightGeom.empty()) lightGeom.assign(16 * lights.size(), 0.f);
-            std::copy(g, g + 16, lightGeom.begin() + 16 * i);
+            if (lightGeom.empty()) lightGeom.assign(24 * lights.size(), 0.f);
+            std::copy(g, g + 24, lightGeom.begin() + 24 * i);
         };
         if (const PointLight *pl = lights[i].CastOrNullptr<PointLight>()) {
             Point3f p = pl->renderFromLight(Point3f(0, 0, 0));
-            float g[16] = {p.x, p.y, p.z};
+            float g[24] = {p.x, p.y, p.z};
             deltaLight(2, pl->I, pl->scale, g);
             continue;
         }
         if (const SpotLight *sl = lights[i].CastOrNullptr<SpotLight>()) {
             Point3f p = sl->renderFromLight(Point3f(0, 0, 0));
             const SquareMatrix<4> &mi = sl->renderFromLight.GetInverseMatrix();
-            float g[16] = {p.x, p.y, p.z, 0.f, mi[0][0], mi[0][1], mi[0][2], mi[1][0], mi[1][1], mi[1][2],
+            float g[24] = {p.x, p.y, p.z, 0.f, mi[0][0], mi[0][1], mi[0][2], mi[1][0], mi[1][1], mi[1][2],
                            mi[2][0], mi[2][1], mi[2][2], sl->cosFalloffStart, sl->cosFalloffEnd, 0.f};
             deltaLight(3, sl->Iemit, sl->scale, g);
             continue;
         }
         if (const DistantLight *dl = lights[i].CastOrNullptr<DistantLight>()) {
             Vector3f wi = Normalize(dl->renderFromLight(Vector3f(0, 0, 1)));
-            float g[16] = {wi.x, wi.y, wi.z, dl->sceneRadius};
+            float g[24] = {wi.x, wi.y, wi.z, dl->sceneRadius};
             deltaLight(4, dl->Lemit, dl->scale, g);
+            continue;
+        }
+        if (const ImageInfiniteLight *il = lights[i].CastOrNullptr<ImageInfiniteLight>()) {
+            // image and sampling distribution: include/b200pt.h b200pt_render_desc::env_image / env_distribution
+            const SquareMatrix<4> &m = il->renderFromLight.GetMatrix(), &mi = il->renderFromLight.GetInverseMatrix();
+            float g[24] = {m[0][0], m[0][1], m[0][2], m[1][0], m[1][1], m[1][2], m[2][0], m[2][1], m[2][2],
+                           mi[0][0], mi[0][1], mi[0][2], mi[1][0], mi[1][1], mi[1][2], mi[2][0], mi[2][1], mi[2][2],
+                           il->sceneRadius};
+            // `spectrum` = the colour space's illuminant, as RGBIlluminantSpectrum samples it (DenselySampledSpectrum)
+            const DenselySampledSpectrum *illum = &il->imageColorSpace->illuminant;
+            deltaLight(5, illum, il->scale, g);
+            const int res = il->image.Resolution().x;
+            std::vector<float> px(size_t(res) * res * 4), dist(size_t(res) * res);
+            for (int y = 0; y < res; ++y)
+                for (int x = 0; x < res; ++x) {
+                    RGB rgb;
+                    for (int c = 0; c < 3; ++c) rgb[c] = il->image.GetChannel({x, y}, c);
+                    RGBIlluminantSpectrum spec(*il->imageColorSpace, ClampZero(rgb));
+                    float *o = &px[(size_t(y) * res + x) * 4];
+                    o[0] = spec.rsp.c0;
+                    o[1] = spec.rsp.c1;
+                    o[2] = spec.rsp.c2;
+                    o[3] = spec.scale;
+                    dist[size_t(y) * res + x] = il->compensatedDistribution.pConditionalV[y].func[x];
+                }
+            w.f32("env_image", {uint32_t(res), uint32_t(res), 4}, px);
+            w.f32("env_distribution", {uint32_t(res), uint32_t(res)}, dist);
             continue;
         }
         const DiffuseAreaLight *al = lights[i].CastOrNullptr<DiffuseAreaLight>();
@@ -756,7 +783,7 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
     }
     w.i32("lights_i", {uint32_t(lights.size()), 7}, lightI);
     w.f32("lights_f", {uint32_t(lights.size()), 6}, lightF);
-    if (!lightGeom.empty()) w.f32("lights_geom", {uint32_t(lights.size()), 16}, lightGeom);
+    if (!lightGeom.empty()) w.f32("lights_geom", {uint32_t(lights.size()), 24}, lightGeom);
 
     // ---- the light BVH (lightsamplers.cpp:109-232), node fields as include/b200pt.h lists them
     if (lsId == 2) {

@@ -241,7 +241,12 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         L.alias = a[4];
         L.type = uint32_t(a[6]);
     }
-    if (T.has("lights_geom")) r.light_geometry = T.at("lights_geom").f();
+    if (T.has("lights_geom")) r.light_geometry = T.at("lights_geom").f();  // B200PT_LIGHT_GEOMETRY_FLOATS columns
+    if (T.has("env_image")) {
+        r.env_image = T.at("env_image").f();
+        r.env_distribution = T.at("env_distribution").f();
+        r.env_resolution = int32_t(T.at("env_distribution").rows());
+    }
     const Table &ma = T.at("mesh_attr");
     const size_t nMesh = ma.rows();
     m.attrs.resize(std::max<size_t>(1, nMesh));

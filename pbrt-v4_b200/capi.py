@@ -12,7 +12,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_NOMEM = 0, 1, 2, 3, 4
 MEM_HOST, MEM_DEVICE = 0, 1
 TRACE_COUNTERS = 1 << 8
 NOALLOC_MAX_RAYS = 1 << 20  # B200PT_NOALLOC_MAX_RAYS
-LIGHT_GEOMETRY_FLOATS = 16  # B200PT_LIGHT_GEOMETRY_FLOATS
+LIGHT_GEOMETRY_FLOATS = 24  # B200PT_LIGHT_GEOMETRY_FLOATS
 MISS = 0xFFFFFFFF
 
 HIT_DTYPE = np.dtype([("mesh", "<u4"), ("prim", "<u4"), ("instance", "<u4"),
@@ -187,7 +187,8 @@ class RenderDesc(C.Structure):
                 ("gbuffer_output_from_render", C.c_float * 16), ("gbuffer_output_from_render_inv", C.c_float * 16),
                 ("material_ids", C.POINTER(C.c_int32)), ("filter_type", C.c_uint32),
                 ("light_geometry", C.POINTER(C.c_float)),
-                ("filter_table", C.POINTER(C.c_float)), ("filter_table_size", C.c_int32 * 2)]
+                ("filter_table", C.POINTER(C.c_float)), ("filter_table_size", C.c_int32 * 2),
+                ("env_image", C.POINTER(C.c_float)), ("env_distribution", C.POINTER(C.c_float)), ("env_resolution", C.c_int32)]
 
 
 GBUFFER_RADIANCE, GBUFFER_POSITION, GBUFFER_MATERIAL, GBUFFER_INSTANCE = 1, 2, 4, 8

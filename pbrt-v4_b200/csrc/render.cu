@@ -281,7 +281,7 @@ GenerateKernel(RenderSceneDev rs, PassBuffers pb, int nPixels, int width, int nA
 }
 
 // ---- hits -> material-sorted queues (the role of EnqueueWorkAfterIntersection, wavefront/intersect.h:67-170)
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)  // the escaped-ray branch (image infinite light) must not set the register count
 ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     int *counts = pb.counts + kCountStride * depth;
@@ -289,9 +289,21 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
     uint32_t slot = pb.hits[6ll * t];
     if (slot == kConsumedTag) return;  // absorbed or scattered in a medium (VolMediumKernel)
     if (slot == kMissTag) {  // escaped: infinite lights add their radiance, the path ends
+        const float *ray = pb.rays[depth & 1] + 7ll * t;
+        auto escapeCtx = [&](int path) {  // the ray and the previous vertex' light-sample context (StoreHeader's layout)
+            const long long n = pb.n;
+            const float *s = pb.scalars + path;
+            EscapeCtx ec;
+            ec.unweighted = depth == 0 || ((uint32_t)pb.ints[3 * n + path] & PF_SPECULAR) != 0;
+            ec.d = mk(ray[3], ray[4], ray[5]);
+            ec.prevP = (mk(s[3 * n], s[4 * n], s[5 * n]) + mk(s[6 * n], s[7 * n], s[8 * n])) / 2;
+            ec.prevNs = mk(s[12 * n], s[13 * n], s[14 * n]);
+            return ec;
+        };
+        const bool lightBvh = rs.integrator.lightSampler == 2;
         if (rs.nInfiniteLights && rs.integrator.type == 1 && pb.rays[depth & 1][7ll * t + 6] >= 0) {
             GlobalIO io(pb, pb.rayPath[depth & 1][t], nullptr);
-            EscapedRadianceVol(rs, pb.scalars[io.path], io);
+            EscapedRadianceVol(rs, pb.scalars[io.path], io, escapeCtx(io.path), lightBvh);
         } else if (rs.nInfiniteLights && pb.rays[depth & 1][7ll * t + 6] >= 0) {
             struct {
                 const PassBuffers &pb;
@@ -300,8 +312,7 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
                 __device__ void AddL(int k, float v) { pb.L[(long long)k * pb.n + path] += v; }
             } io{pb, pb.rayPath[depth & 1][t]};
             const long long n = pb.n;
-            uint32_t flags = (uint32_t)pb.ints[3 * n + io.path];
-            EscapedRadiance(rs, pb.scalars[io.path], depth == 0 || (flags & PF_SPECULAR), pb.scalars[2 * n + io.path], io);
+            EscapedRadiance(rs, pb.scalars[io.path], pb.scalars[2 * n + io.path], io, escapeCtx(io.path), lightBvh);
         }
         return;
     }

@@ -22,7 +22,7 @@ struct b200pt_render {
     RenderHost host;
     RenderSceneDev dev{};
     void *dSpectra = nullptr, *dMaterials = nullptr, *dLights = nullptr, *dMeshes = nullptr;
-    void *dLightBvh = nullptr, *dBitTrails = nullptr, *dInfinite = nullptr, *dLightGeom = nullptr, *dFilterTable = nullptr;
+    void *dLightBvh = nullptr, *dBitTrails = nullptr, *dInfinite = nullptr, *dLightGeom = nullptr, *dFilterTable = nullptr, *dEnvImage = nullptr, *dEnvDist = nullptr;
     void *dLens = nullptr, *dPupil = nullptr, *dCornerAttr = nullptr, *dMaterialIds = nullptr;
     float *dFilmIds = nullptr;  // GBufferFilm: materialId / instanceId of the last sample per pixel (2 x nPixels)
     void *dMedia = nullptr;
@@ -74,6 +74,8 @@ int b200pt_render_destroy(b200pt_render *r) {
     cudaFree(r->dInfinite);
     cudaFree(r->dLightGeom);
     cudaFree(r->dFilterTable);
+    cudaFree(r->dEnvImage);
+    cudaFree(r->dEnvDist);
     cudaFree(r->dLens);
     cudaFree(r->dMedia);
     for (void *g : r->dGrids) cudaFree(g);
@@ -116,7 +118,8 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         (rc = Upload(ctx, r->host.infiniteLights, &r->dInfinite)) || (rc = Upload(ctx, r->host.lens, &r->dLens)) ||
         (rc = Upload(ctx, r->host.pupilBounds, &r->dPupil)) || (rc = Upload(ctx, r->host.cornerAttr, &r->dCornerAttr)) ||
         (rc = Upload(ctx, r->host.materialIds, &r->dMaterialIds)) || (rc = Upload(ctx, r->host.lightGeom, &r->dLightGeom)) ||
-        (rc = Upload(ctx, r->host.filterTable, &r->dFilterTable)))
+        (rc = Upload(ctx, r->host.filterTable, &r->dFilterTable)) || (rc = Upload(ctx, r->host.envImage, &r->dEnvImage)) ||
+        (rc = Upload(ctx, r->host.envDist, &r->dEnvDist)))
         return fail(rc);
     for (size_t i = 0; i < r->host.media.size(); ++i) {  // grids first: the medium table points at them
         if (r->host.media[i].type != 1) continue;
@@ -142,6 +145,8 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
     r->dev.infiniteLights = (const int32_t *)r->dInfinite;
     r->dev.lightGeom = r->host.lightGeom.empty() ? nullptr : (const float *)r->dLightGeom;
     r->dev.film.filterTable = r->host.filterTable.empty() ? nullptr : (const float *)r->dFilterTable;
+    r->dev.envImage = (const float *)r->dEnvImage;
+    r->dev.envDist = (const float *)r->dEnvDist;
     r->dev.camera.lens = (const float *)r->dLens;
     r->dev.camera.pupilBounds = (const float *)r->dPupil;
     r->dev.cornerAttr = (const float *)r->dCornerAttr;

@@ -203,6 +203,27 @@ B2_HD float SamplePiecewise1D(const float *cdf, int n, float lo, float hi, float
     if (cdf[o + 1] - cdf[o] > 0) du /= cdf[o + 1] - cdf[o];
     return Lerp((o + du) / n, lo, hi);
 }
+// PiecewiseConstant2D::Sample (util/sampling.h:752-762) over a table f[ny][nx] | conditional cdf[ny][nx + 1] |
+// conditional funcInt[ny] | marginal cdf[ny + 1] | marginal funcInt, domain [lox, hix] x [loy, hiy]
+B2_HD void SamplePiecewise2D(const float *f, int nx, int ny, float lox, float hix, float loy, float hiy, float u0, float u1,
+                             float &x, float &y, float &pdf, int &iu, int &iv) {
+    const float *condCdf = f + nx * ny, *condInt = condCdf + ny * (nx + 1);
+    const float *margCdf = condInt + ny, margInt = margCdf[ny + 1];
+    y = SamplePiecewise1D(margCdf, ny, loy, hiy, u1, &iv);
+    float pdf1 = margInt > 0 ? condInt[iv] / margInt : 0.f;
+    x = SamplePiecewise1D(condCdf + iv * (nx + 1), nx, lox, hix, u0, &iu);
+    float pdf0 = condInt[iv] > 0 ? fabsf(f[iv * nx + iu]) / condInt[iv] : 0.f;
+    pdf = pdf0 * pdf1;
+}
+// PiecewiseConstant2D::PDF (util/sampling.h:764-771) for p already in [0, 1]^2 of the domain
+B2_HD float Piecewise2DPDF(const float *f, int nx, int ny, float px, float py) {
+    int iu = (int)(px * nx), iv = (int)(py * ny);
+    iu = iu < 0 ? 0 : (iu > nx - 1 ? nx - 1 : iu);
+    iv = iv < 0 ? 0 : (iv > ny - 1 ? ny - 1 : iv);
+    const float margInt = f[nx * ny + ny * (nx + 1) + ny + ny + 1];
+    return fabsf(f[iv * nx + iu]) / margInt;
+}
+
 // Filter::Sample(u): BoxFilter (filters.h:60-64), or FilterSampler::Sample (filters.h:27-33): the point from the
 // tabulated distribution (PiecewiseConstant2D::Sample, util/sampling.h:752-762), weight f[cell] / pdf
 B2_HD void SampleFilter(const FilmDev &film, float u0, float u1, float &fx, float &fy, float &weight) {
@@ -213,15 +234,11 @@ B2_HD void SampleFilter(const FilmDev &film, float u0, float u1, float &fx, floa
         return;
     }
     const int nx = film.filterNx, ny = film.filterNy;
-    const float *f = film.filterTable, *condCdf = f + nx * ny, *condInt = condCdf + ny * (nx + 1);
-    const float *margCdf = condInt + ny, margInt = margCdf[ny + 1];
     int iv, iu;
-    fy = SamplePiecewise1D(margCdf, ny, -film.filterRadiusY, film.filterRadiusY, u1, &iv);
-    float pdf1 = margInt > 0 ? condInt[iv] / margInt : 0.f;
-    fx = SamplePiecewise1D(condCdf + iv * (nx + 1), nx, -film.filterRadiusX, film.filterRadiusX, u0, &iu);
-    float fv = f[iv * nx + iu];
-    float pdf0 = condInt[iv] > 0 ? fabsf(fv) / condInt[iv] : 0.f;
-    weight = fv / (pdf0 * pdf1);
+    float pdf;
+    SamplePiecewise2D(film.filterTable, nx, ny, -film.filterRadiusX, film.filterRadiusX, -film.filterRadiusY,
+                      film.filterRadiusY, u0, u1, fx, fy, pdf, iu, iv);
+    weight = film.filterTable[iv * nx + iu] / pdf;
 }
 
 // ------------------------------------------------------------------ wavelengths and spectra

@@ -7,6 +7,23 @@
 
 namespace b200pt {
 
+// PiecewiseConstant2D(f, domain) (util/sampling.h:731-747) out of PiecewiseConstant1D's (:625-649), in float as there.
+// Layout: f[ny][nx] | conditional cdf[ny][nx + 1] | conditional funcInt[ny] | marginal cdf[ny + 1] | marginal funcInt
+static void BuildPiecewise2D(const float *f, int nx, int ny, float lox, float hix, float loy, float hiy, std::vector<float> &t) {
+    t.assign(size_t(nx) * ny + size_t(ny) * (nx + 1) + ny + (ny + 1) + 1, 0.f);
+    std::copy(f, f + size_t(nx) * ny, t.begin());
+    float *condCdf = t.data() + size_t(nx) * ny, *condInt = condCdf + size_t(ny) * (nx + 1), *margCdf = condInt + ny;
+    auto build = [](const float *func, int n, float lo, float hi, float *cdf) {  // returns funcInt
+        cdf[0] = 0;
+        for (int i = 1; i < n + 1; ++i) cdf[i] = cdf[i - 1] + std::abs(func[i - 1]) * (hi - lo) / n;
+        float funcInt = cdf[n];
+        for (int i = 1; i < n + 1; ++i) cdf[i] = funcInt == 0 ? float(i) / float(n) : cdf[i] / funcInt;
+        return funcInt;
+    };
+    for (int v = 0; v < ny; ++v) condInt[v] = build(f + size_t(v) * nx, nx, lox, hix, condCdf + size_t(v) * (nx + 1));
+    margCdf[ny + 1] = build(condInt, ny, loy, hiy, margCdf);
+}
+
 static int Log2Int(uint32_t v) {
     int l = 0;
     while (v >>= 1) ++l;
@@ -52,21 +69,8 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         if (!(d->filter_radius[0] > 0) || !(d->filter_radius[1] > 0)) return bad("filter radius must be positive");
         for (int i = 0; i < nx * ny; ++i)
             if (!std::isfinite(d->filter_table[i])) return bad("filter_table holds a non-finite value");
-        // PiecewiseConstant2D(f, domain) (util/sampling.h:731-747) out of PiecewiseConstant1D's (:625-649), in float as there
-        std::vector<float> &t = out.filterTable;
-        t.assign(size_t(nx) * ny + size_t(ny) * (nx + 1) + ny + (ny + 1) + 1, 0.f);
-        std::copy(d->filter_table, d->filter_table + size_t(nx) * ny, t.begin());
-        float *condCdf = t.data() + size_t(nx) * ny, *condInt = condCdf + size_t(ny) * (nx + 1), *margCdf = condInt + ny;
-        auto build = [](const float *func, int n, float lo, float hi, float *cdf) {  // returns funcInt
-            cdf[0] = 0;
-            for (int i = 1; i < n + 1; ++i) cdf[i] = cdf[i - 1] + std::abs(func[i - 1]) * (hi - lo) / n;
-            float funcInt = cdf[n];
-            for (int i = 1; i < n + 1; ++i) cdf[i] = funcInt == 0 ? float(i) / float(n) : cdf[i] / funcInt;
-            return funcInt;
-        };
-        for (int v = 0; v < ny; ++v)
-            condInt[v] = build(d->filter_table + size_t(v) * nx, nx, -d->filter_radius[0], d->filter_radius[0], condCdf + size_t(v) * (nx + 1));
-        margCdf[ny + 1] = build(condInt, ny, -d->filter_radius[1], d->filter_radius[1], margCdf);
+        BuildPiecewise2D(d->filter_table, nx, ny, -d->filter_radius[0], d->filter_radius[0], -d->filter_radius[1],
+                         d->filter_radius[1], out.filterTable);
     }
     if (d->film_type > 2) return bad("unsupported film type");
     if (d->film_type == 2 && (d->n_buckets != 31 || d->lambda_min != 395.f || d->lambda_max != 705.f))
@@ -300,9 +304,24 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     for (uint32_t i = 0; i < d->n_lights; ++i)
         if (d->lights[i].type >= B200PT_LIGHT_POINT) out.rs.geomExt = 1u;
     out.lights.resize(d->n_lights);
+    out.rs.envLight = -1;
+    out.rs.envRes = 0;
+    out.rs.envImage = out.rs.envDist = nullptr;  // filled by the owner of the storage
     for (uint32_t i = 0; i < d->n_lights; ++i) {
         const b200pt_light &l = d->lights[i];
-        if (l.type > B200PT_LIGHT_DISTANT) return bad("unsupported light type");
+        if (l.type > B200PT_LIGHT_IMAGE_INFINITE) return bad("unsupported light type");
+        if (l.type == B200PT_LIGHT_IMAGE_INFINITE) {
+            if (out.rs.envLight >= 0) return bad("one image infinite light per scene");
+            const int res = d->env_resolution;
+            if (!d->env_image || !d->env_distribution || res < 1 || res > 16384)
+                return bad("an image infinite light needs env_image, env_distribution and env_resolution");
+            for (size_t k = 0; k < size_t(res) * res; ++k)
+                if (!std::isfinite(d->env_distribution[k]) || d->env_distribution[k] < 0) return bad("env_distribution must be finite and >= 0");
+            out.rs.envLight = int32_t(i);
+            out.rs.envRes = res;
+            out.envImage.assign(d->env_image, d->env_image + 4 * size_t(res) * res);
+            BuildPiecewise2D(d->env_distribution, res, res, 0.f, 1.f, 0.f, 1.f, out.envDist);
+        }
         if (l.type >= B200PT_LIGHT_POINT) {
             if (!d->light_geometry) return bad("point / spot / distant lights need light_geometry");
             if (out.lightGeom.empty()) out.lightGeom.assign(size_t(kLightGeomFloats) * d->n_lights, 0.f);
@@ -316,7 +335,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
             auto it = slotOf.find((uint64_t(l.mesh) << 32) | l.tri);
             if (it == slotOf.end()) return bad("light refers to a triangle that is not in the scene");
             slot = it->second;
-        } else if (l.type == B200PT_LIGHT_UNIFORM_INFINITE || l.type == B200PT_LIGHT_DISTANT)
+        } else if (l.type == B200PT_LIGHT_UNIFORM_INFINITE || l.type == B200PT_LIGHT_DISTANT || l.type == B200PT_LIGHT_IMAGE_INFINITE)
             out.infiniteLights.push_back(int32_t(i));  // Light::Bounds() is empty (lightsamplers.cpp:114-123)
         if (!specOk(l.spectrum)) return bad("light spectrum index out of range");
         if (l.alias >= int32_t(d->n_lights)) return bad("alias index out of range");

@@ -20,6 +20,7 @@ struct RenderHost {
     std::vector<uint32_t> lightBvhNodes;   // 8 per node
     std::vector<uint32_t> lightBitTrails;  // per light
     std::vector<int32_t> infiniteLights;   // light indices: the lights without bounds (BVHLightSampler's infiniteLights)
+    std::vector<float> envImage, envDist;  // image infinite light: per-pixel spectrum coefficients, sampling distribution
     std::vector<float> filterTable;        // FilmDev::filterTable (empty: box filter)
     std::vector<float> lightGeom;          // delta lights' placement, kLightGeomFloats per light; empty = none
     std::vector<MediumDev> media;          // density / majorants pointers are filled by the owner of the grids

@@ -273,14 +273,49 @@ B2_HD float AvgRuRl(const IO &io) {
     return sum / kNLambda;
 }
 
-// VolPathIntegrator's escaped ray (cpu/integrators.cpp:1081-1099): beta * Le / r_u.Average(); with MIS r_l is first
-// scaled by the light's p_l, which is 0 for a UniformInfiniteLight under allowIncompletePDF, so the weight is the same.
+// What an escaped ray needs for the MIS weight of an infinite light that light sampling can also pick (an image
+// infinite light; a uniform one has PDF_Li = 0 under allowIncompletePDF): the ray's direction and the previous
+// vertex' light-sample context.
+struct EscapeCtx {
+    bool unweighted;  // the ray left the camera or a specular bounce
+    V3 d, prevP, prevNs;
+};
+// LightSampler::PMF(ctx, light) for the scene's sampler (lightsamplers.h:48-53, 78-82, 320-358)
+B2_HD float LightPMF(const RenderSceneDev &rs, bool lightBvh, V3 p, V3 ns, int light) {
+    if (lightBvh) return LightBvhPMF(rs, p, ns, light);
+    if (rs.integrator.lightSampler == 0) return 1.f / rs.nLights;
+    return rs.lights[light].aliasP;
+}
+
+// VolPathIntegrator's escaped ray (cpu/integrators.cpp:1081-1099): beta * Le / r_u.Average() from the camera or a
+// specular bounce; else r_l is first scaled by the light's p_l (0 for a UniformInfiniteLight under allowIncompletePDF)
+// and the estimate is beta * Le / (r_u + r_l).Average().
 template <class IO>
-B2_HD void EscapedRadianceVol(const RenderSceneDev &rs, float lambdaU, IO &io) {
-    const float avg = AvgRu(io);
+B2_HD void EscapedRadianceVol(const RenderSceneDev &rs, float lambdaU, IO &io, const EscapeCtx &ec, bool lightBvh) {
     for (uint32_t i = 0; i < rs.nInfiniteLights; ++i) {
-        const LightDev &light = rs.lights[rs.infiniteLights[i]];
+        const int lidx = rs.infiniteLights[i];
+        const LightDev &light = rs.lights[lidx];
+        if (light.type == LIGHT_IMAGE_INFINITE) {
+            const float *g = rs.lightGeom + size_t(kLightGeomFloats) * lidx;
+            const int pixel = EnvPixelOfRay(rs, g, ec.d);
+            float avg;
+            if (ec.unweighted)
+                avg = AvgRu(io);
+            else {
+                float p_l = LightPMF(rs, lightBvh, ec.prevP, ec.prevNs, lidx) * EnvPDF(rs, g, ec.d);
+                for (int k = 0; k < kNLambda; ++k) io.SetRl(k, io.Rl(k) * p_l);
+                avg = AvgRuRl(io);
+            }
+            LambdaIter li(lambdaU);
+B2_SPECTRAL_LOOP
+            for (int k = 0; k < kNLambda; ++k, li.Next()) {
+                float Le = EnvLe(rs, light, pixel, li.lam);
+                if (Le != 0) io.AddL(k, io.Beta(k) * Le / avg);
+            }
+            continue;
+        }
         if (light.type != LIGHT_UNIFORM_INFINITE) continue;  // a DistantLight: in the sampler's list, LightType::DeltaDirection
+        const float avg = AvgRu(io);
         const SpectrumTable &sp = rs.spectra[light.spectrum];
         LambdaIter li(lambdaU);
 B2_SPECTRAL_LOOP
@@ -293,19 +328,25 @@ B2_SPECTRAL_LOOP
 
 // Escaped ray: every infinite light adds beta * Le, MIS-weighted against light sampling unless the ray
 // left the camera or a specular bounce (cpu/integrators.cpp:645-662).  UniformInfiniteLight::PDF_Li is 0
-// under allowIncompletePDF (lights.cpp:998-1003), so the weight is PowerHeuristic(p_b, 0).
+// under allowIncompletePDF (lights.cpp:998-1003), so its weight is PowerHeuristic(p_b, 0).
 template <class IO>
-B2_HD void EscapedRadiance(const RenderSceneDev &rs, float lambdaU, bool unweighted, float pB, IO &io) {
+B2_HD void EscapedRadiance(const RenderSceneDev &rs, float lambdaU, float pB, IO &io, const EscapeCtx &ec, bool lightBvh) {
     for (uint32_t i = 0; i < rs.nInfiniteLights; ++i) {
-        const LightDev &light = rs.lights[rs.infiniteLights[i]];
-        if (light.type != LIGHT_UNIFORM_INFINITE) continue;
+        const int lidx = rs.infiniteLights[i];
+        const LightDev &light = rs.lights[lidx];
+        if (light.type != LIGHT_UNIFORM_INFINITE && light.type != LIGHT_IMAGE_INFINITE) continue;
+        const bool env = light.type == LIGHT_IMAGE_INFINITE;
+        const float *g = rs.lightGeom + size_t(kLightGeomFloats) * lidx;
+        const int pixel = env ? EnvPixelOfRay(rs, g, ec.d) : 0;
+        float p_l = 0;
+        if (env && !ec.unweighted) p_l = LightPMF(rs, lightBvh, ec.prevP, ec.prevNs, lidx) * EnvPDF(rs, g, ec.d);
         const SpectrumTable &sp = rs.spectra[light.spectrum];
-        float w = unweighted ? 1.f : PowerHeuristic(pB, 0.f);
+        float w = ec.unweighted ? 1.f : PowerHeuristic(pB, p_l);
         LambdaIter li(lambdaU);
 B2_SPECTRAL_LOOP
         for (int k = 0; k < kNLambda; ++k, li.Next()) {
-            float Le = light.scale * SpectrumAt(sp, li.lam);
-            io.AddL(k, unweighted ? io.Beta(k) * Le : io.Beta(k) * w * Le);
+            float Le = env ? EnvLe(rs, light, pixel, li.lam) : light.scale * SpectrumAt(sp, li.lam);
+            io.AddL(k, ec.unweighted ? io.Beta(k) * Le : io.Beta(k) * w * Le);
         }
     }
 }
@@ -325,10 +366,11 @@ B2_HD void ShadeVertex(const RenderSceneDev &rs, PathRegs &p, const uint32_t hit
     const bool vol = VOL < 0 ? rs.integrator.type == 1 : VOL == 1;
     if (hit[0] == kMissTag) {  // escaped ray (cpu/integrators.cpp:645-662); the kernels do this in ClassifyKernel
         if (rs.nInfiniteLights) {
+            EscapeCtx ec{p.depth == 0 || (p.flags & PF_SPECULAR) != 0, p.rayD, Mid(p.prev.pi), p.prev.ns};
             if (vol)
-                EscapedRadianceVol(rs, p.lambdaU, io);
+                EscapedRadianceVol(rs, p.lambdaU, io, ec, lightBvh);
             else
-                EscapedRadiance(rs, p.lambdaU, p.depth == 0 || (p.flags & PF_SPECULAR), p.pB, io);
+                EscapedRadiance(rs, p.lambdaU, p.pB, io, ec, lightBvh);
         }
         KillPath(p);
         return;
@@ -497,15 +539,19 @@ B2_SPECTRAL_LOOP
             }
             V3 cp = Mid(ctx.pi);
             // the delta lights (point, spot, distant): pdf 1, no MIS (cpu/integrators.cpp:798-799, 1386-1387)
-            const bool delta = EXT && lidx >= 0 && light.type >= LIGHT_POINT;
+            const bool delta = EXT && lidx >= 0 && light.type >= LIGHT_POINT && light.type <= LIGHT_DISTANT;
             V3 wiDelta = mk(0, 0, 0);
             float attenDelta = 1.f;
             if (delta) SampleDeltaLight(light, rs.lightGeom + size_t(kLightGeomFloats) * lidx, cp, ss, wiDelta, attenDelta);
+            // an image infinite light: direction from its compensated distribution, MIS as for an area light
+            const bool env = EXT && lidx >= 0 && light.type == LIGHT_IMAGE_INFINITE;
+            int envPixel = 0;
+            if (env) SampleEnvLight(rs, rs.lightGeom + size_t(kLightGeomFloats) * lidx, cp, uLight0, uLight1, ss, wiDelta, envPixel);
             if (ss.ok && ss.pdf != 0 && LengthSquared(Mid(ss.pi) - cp) != 0) {
-                V3 wi = delta ? wiDelta : Normalize(Mid(ss.pi) - cp);
-                if (delta || AreaLightEmits(light, ss.n, -wi)) {
+                V3 wi = (delta || env) ? wiDelta : Normalize(Mid(ss.pi) - cp);
+                if (delta || env || AreaLightEmits(light, ss.n, -wi)) {
                     float atten = attenDelta;
-                    if (!delta && light.cosFalloffEnd > 0) {  // ISET spread angle (lights.cpp:762-770)
+                    if (!delta && !env && light.cosFalloffEnd > 0) {  // ISET spread angle (lights.cpp:762-770)
                         float cos_a = -DotN(ss.n, wi);
                         float sin_a = SafeSqrt(1 - SqrF(cos_a));
                         float tan_a = sin_a / cos_a;
@@ -525,7 +571,7 @@ B2_SPECTRAL_LOOP
                         LambdaIter li(p.lambdaU);
 B2_SPECTRAL_LOOP
                         for (int k = 0; k < kNLambda; ++k, li.Next()) {
-                            float Le = light.scale * SpectrumAt(sp, li.lam) * atten;
+                            float Le = env ? EnvLe(rs, light, envPixel, li.lam) : light.scale * SpectrumAt(sp, li.lam) * atten;
                             float f = BsdfSpectral<EXT>(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f, k, spec8) * absCos;
                             // volpath keeps beta * f_hat * L; the transmittance walk supplies T_ray and the MIS weight
                             io.SetLd(k, vol ? io.Beta(k) * f * Le : io.Beta(k) * (w_l * Le * f / p_l));

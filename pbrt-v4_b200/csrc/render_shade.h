@@ -277,6 +277,110 @@ B2_HD bool SampleDeltaLight(const LightDev &light, const float *g, V3 cp, ShapeS
     return true;
 }
 
+// ---- ImageInfiniteLight (lights.h:557-643, lights.cpp:1038-1083): an equal-area square image of the sphere
+// EqualAreaSquareToSphere / EqualAreaSphereToSquare (util/math.cpp:292-361)
+B2_HD V3 EqualAreaSquareToSphere(float px, float py) {
+    float u = 2 * px - 1, v = 2 * py - 1;
+    float up = fabsf(u), vp = fabsf(v);
+    float signedDistance = 1 - (up + vp);
+    float d = fabsf(signedDistance);
+    float r = 1 - d;
+    float phi = (r == 0 ? 1 : (vp - up) / r + 1) * kPi / 4;
+    float z = copysignf(1 - SqrF(r), signedDistance);
+    float cosPhi = copysignf(cosf(phi), u);
+    float sinPhi = copysignf(sinf(phi), v);
+    return mk(cosPhi * r * SafeSqrt(2 - SqrF(r)), sinPhi * r * SafeSqrt(2 - SqrF(r)), z);
+}
+B2_HD void EqualAreaSphereToSquare(V3 d, float &pu, float &pv) {
+    float x = fabsf(d.x), y = fabsf(d.y), z = fabsf(d.z);
+    float r = SafeSqrt(1 - z);
+    float a = fmaxf(x, y), b = fminf(x, y);
+    b = a == 0 ? 0 : b / a;
+    // EvaluatePolynomial(b, t1 .. t7) (util/math.h): Horner with fused multiply-adds
+    const float t1 = 0.406758566246788489601959989e-5f, t2 = 0.636226545274016134946890922156f,
+                t3 = 0.61572017898280213493197203466e-2f, t4 = -0.247333733281268944196501420480f,
+                t5 = 0.881770664775316294736387951347e-1f, t6 = 0.419038818029165735901852432784e-1f,
+                t7 = -0.251390972343483509333252996350e-1f;
+    float phi = FMAf(b, FMAf(b, FMAf(b, FMAf(b, FMAf(b, FMAf(b, t7, t6), t5), t4), t3), t2), t1);
+    if (x < y) phi = 1 - phi;
+    float v = phi * r;
+    float u = r - v;
+    if (d.z < 0) {  // southern hemisphere: mirror
+        float t = u;
+        u = v;
+        v = t;
+        u = 1 - u;
+        v = 1 - v;
+    }
+    u = copysignf(u, d.x);
+    v = copysignf(v, d.y);
+    pu = 0.5f * (u + 1);
+    pv = 0.5f * (v + 1);
+}
+// Image::LookupNearestChannel(uv, c, WrapMode::OctahedralSphere) (util/image.h:352-356, 100-125): the pixel
+B2_HD int EnvPixel(int res, float pu, float pv) {
+    int x = (int)(pu * res), y = (int)(pv * res);
+    if (x < 0) {
+        x = -x;
+        y = res - 1 - y;
+    } else if (x >= res) {
+        x = 2 * res - 1 - x;
+        y = res - 1 - y;
+    }
+    if (y < 0) {
+        x = res - 1 - x;
+        y = -y;
+    } else if (y >= res) {
+        x = res - 1 - x;
+        y = 2 * res - 1 - y;
+    }
+    if (res == 1) x = y = 0;
+    return y * res + x;
+}
+// ImageLe (lights.h:626-633) at one wavelength: scale * RGBIlluminantSpectrum(rgb)(lambda) = scale * (s * S(poly(lambda))) *
+// illuminant(lambda), RGBSigmoidPolynomial (util/color.h) with the pixel's coefficients
+B2_HD float EnvLe(const RenderSceneDev &rs, const LightDev &light, int pixel, float lam) {
+    const float *c = rs.envImage + 4ll * pixel;
+    float x = FMAf(lam, FMAf(lam, c[0], c[1]), c[2]);
+    float s = std::isinf(x) ? (x > 0 ? 1.f : 0.f) : .5f + x / (2 * sqrtf(1 + SqrF(x)));
+    return light.scale * ((c[3] * s) * SpectrumAt(rs.spectra[light.spectrum], lam));
+}
+// ImageInfiniteLight::SampleLi under allowIncompletePDF (lights.h:597-621): direction from the compensated distribution
+B2_HD bool SampleEnvLight(const RenderSceneDev &rs, const float *g, V3 cp, float u0, float u1, ShapeSampleOut &ss, V3 &wi,
+                          int &pixel) {
+    float pu, pv, mapPDF;
+    int iu, iv;
+    SamplePiecewise2D(rs.envDist, rs.envRes, rs.envRes, 0.f, 1.f, 0.f, 1.f, u0, u1, pu, pv, mapPDF, iu, iv);
+    ss.ok = false;
+    if (mapPDF == 0) return false;
+    V3 wl = EqualAreaSquareToSphere(pu, pv);
+    wi = mk(g[0] * wl.x + g[1] * wl.y + g[2] * wl.z, g[3] * wl.x + g[4] * wl.y + g[5] * wl.z,
+            g[6] * wl.x + g[7] * wl.y + g[8] * wl.z);
+    ss.pdf = mapPDF / (4 * kPi);
+    ss.n = mk(0, 0, 0);
+    ss.pi = MakeP3i(cp + wi * (2 * g[18]), mk(0, 0, 0));
+    ss.ok = true;
+    pixel = EnvPixel(rs.envRes, pu, pv);
+    return true;
+}
+// the light-space direction of a render-space one: renderFromLight.ApplyInverse(w)
+B2_HD V3 EnvLightDir(const float *g, V3 w) {
+    return mk(g[9] * w.x + g[10] * w.y + g[11] * w.z, g[12] * w.x + g[13] * w.y + g[14] * w.z,
+              g[15] * w.x + g[16] * w.y + g[17] * w.z);
+}
+// ImageInfiniteLight::PDF_Li(ctx, w, allowIncompletePDF = true) (lights.cpp:1073-1083)
+B2_HD float EnvPDF(const RenderSceneDev &rs, const float *g, V3 w) {
+    float pu, pv;
+    EqualAreaSphereToSquare(EnvLightDir(g, w), pu, pv);
+    return Piecewise2DPDF(rs.envDist, rs.envRes, rs.envRes, pu, pv) / (4 * kPi);
+}
+// the pixel ImageInfiniteLight::Le(ray) reads (lights.h:589-593)
+B2_HD int EnvPixelOfRay(const RenderSceneDev &rs, const float *g, V3 d) {
+    float pu, pv;
+    EqualAreaSphereToSquare(Normalize(EnvLightDir(g, d)), pu, pv);
+    return EnvPixel(rs.envRes, pu, pv);
+}
+
 B2_HD float TriArea(const TriVerts &t) { return 0.5f * Length(Cross(t.p1 - t.p0, t.p2 - t.p0)); }  // shapes.h:866-871
 
 // Triangle::Sample(u) by area (shapes.h:1012-1047)

@@ -45,11 +45,13 @@ struct LightDev {
     uint32_t flipNormal; // mesh reverseOrientation ^ transformSwapsHandedness
 };
 
-enum : uint32_t { LIGHT_AREA = 0, LIGHT_UNIFORM_INFINITE = 1, LIGHT_POINT = 2, LIGHT_SPOT = 3, LIGHT_DISTANT = 4 };
+enum : uint32_t { LIGHT_AREA = 0, LIGHT_UNIFORM_INFINITE = 1, LIGHT_POINT = 2, LIGHT_SPOT = 3, LIGHT_DISTANT = 4,
+                  LIGHT_IMAGE_INFINITE = 5 };
 // lightGeom record of light i: [0..2] point / spot: renderFromLight(0,0,0); distant: Normalize(renderFromLight(0,0,1));
 // [3] distant: sceneRadius (DistantLight::Preprocess, lights.h:277-279); [4..12] spot: the upper 3 x 3 of
-// renderFromLight's inverse, row-major; [13] cosFalloffStart, [14] cosFalloffEnd (lights.cpp:1376-1385); [15] 0
-constexpr int kLightGeomFloats = 16;
+// renderFromLight's inverse, row-major; [13] cosFalloffStart, [14] cosFalloffEnd (lights.cpp:1376-1385).
+// Image infinite light: [0..8] the upper 3 x 3 of renderFromLight, [9..17] of its inverse, [18] sceneRadius.
+constexpr int kLightGeomFloats = 24;
 
 struct MeshAttrDev {
     int32_t material;
@@ -155,6 +157,13 @@ struct RenderSceneDev {
                               // variant (thin dielectric, diffuse transmission), the independent sampler or a delta light:
                               // the EXT = 1 kernels run; else the EXT = 0 ones, which carry none of those branches
     const float *cornerAttr;  // per-corner normals / uv of the meshes that have them (MeshAttrDev::nOff, uvOff)
+    // ImageInfiniteLight (lights.h:557-643), at most one per scene: per pixel of its equal-area square image the
+    // RGBIlluminantSpectrum's {c0, c1, c2, scale} (util/spectrum.h RGBSigmoidPolynomial), and the compensated sampling
+    // distribution in the layout of FilmDev::filterTable: f[res][res] | conditional cdf | conditional funcInt | marginal
+    // cdf | marginal funcInt
+    const float *envImage;
+    const float *envDist;
+    int32_t envRes, envLight;  // resolution; index of the light (-1: none)
     const float *lightGeom;   // delta lights' placement (kLightGeomFloats per light, all lights), or null when there are none
     const int32_t *materialIds;  // GBufferFilm: the host's Material::materialId per material (materials.cpp:738), or null
 };

@@ -39,6 +39,8 @@ B2_HD int MediumAfter(const MeshAttrDev &mesh, V3 n, V3 w, int rayMedium) {
 
 // LightSampler::Sample + Light::SampleLi for a reference point (the light half of SampleLd, cpu/integrators.cpp:1290-1303)
 struct LightPick {
+    bool env;        // an image infinite light: its radiance comes from pixel envPixel
+    int envPixel;
     bool ok, delta;  // delta: pdf 1 and no MIS against phase-function sampling (cpu/integrators.cpp:1386-1387)
     int lidx;
     float pmf, atten;
@@ -51,6 +53,8 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
     LightPick lp;
     lp.ok = false;
     lp.delta = false;
+    lp.env = false;
+    lp.envPixel = 0;
     lp.atten = 1.f;
     if (rs.nLights == 0) return lp;
     int nl = (int)rs.nLights;
@@ -67,12 +71,17 @@ B2_HD LightPick PickAndSampleLight(const RenderSceneDev &rs, const LightCtx &ctx
     }
     if (lp.lidx < 0) return lp;
     const LightDev &light = rs.lights[lp.lidx];
-    if (EXT && light.type >= LIGHT_POINT) {  // point, spot, distant
+    if (EXT && light.type >= LIGHT_POINT && light.type <= LIGHT_DISTANT) {  // point, spot, distant
         lp.delta = true;
         lp.ok = SampleDeltaLight(light, rs.lightGeom + size_t(kLightGeomFloats) * lp.lidx, Mid(ctx.pi), lp.ss, lp.wi, lp.atten);
         return lp;
     }
-    if (light.type != 0) return lp;  // infinite lights give nothing under allowIncompletePDF
+    if (EXT && light.type == LIGHT_IMAGE_INFINITE) {
+        lp.ok = SampleEnvLight(rs, rs.lightGeom + size_t(kLightGeomFloats) * lp.lidx, Mid(ctx.pi), u0, u1, lp.ss, lp.wi, lp.envPixel);
+        lp.env = lp.ok;
+        return lp;
+    }
+    if (light.type != 0) return lp;  // a uniform infinite light gives nothing under allowIncompletePDF
     TriVerts lt = LoadTri(rs.prims, light.slot);
     lp.ss = SampleShapeSolidAngle<EXT>(rs.prims, light.slot, lt, ctx, u0, u1, light.flipNormal != 0, CornersOf(rs, rs.meshes[lt.mesh], lt.tri, lt.kind).n);
     V3 cp = Mid(ctx.pi);
@@ -221,7 +230,7 @@ B2_SPECTRAL_LOOP
             LambdaIter li(p.lambdaU);
 B2_SPECTRAL_LOOP
             for (int k = 0; k < kNLambda; ++k, li.Next()) {
-                float Le = light.scale * SpectrumAt(sp, li.lam) * lp.atten;
+                float Le = lp.env ? EnvLe(rs, light, lp.envPixel, li.lam) : light.scale * SpectrumAt(sp, li.lam) * lp.atten;
                 io.SetLd(k, io.Beta(k) * fHat * Le);
                 anyL |= Le != 0;
             }

@@ -138,8 +138,15 @@ class RenderScene:
             lights[i] = capi.Light(max(int(li[0]), 0), max(int(li[1]), 0), int(li[2]), float(lf[0]), int(li[3]),
                                    float(lf[1]), float(lf[2]), float(lf[3]), float(lf[4]), float(lf[5]), int(li[4]),
                                    ltype)
+        if "env_image" in d:  # image infinite light: per-pixel spectrum coefficients [res, res, 4], distribution [res, res]
+            ei, ed = np.ascontiguousarray(d["env_image"], np.float32), np.ascontiguousarray(d["env_distribution"], np.float32)
+            keep += [ei, ed]
+            r.env_image, r.env_distribution = (a.ctypes.data_as(C.POINTER(C.c_float)) for a in (ei, ed))
+            r.env_resolution = ed.shape[0]
         if "lights_geom" in d:  # point / spot / distant lights: their placement (b200pt_render_desc::light_geometry)
-            geom = np.ascontiguousarray(d["lights_geom"], np.float32).reshape(nl, capi.LIGHT_GEOMETRY_FLOATS)
+            geom = np.ascontiguousarray(d["lights_geom"], np.float32).reshape(nl, -1)
+            if geom.shape[1] < capi.LIGHT_GEOMETRY_FLOATS:  # 16 columns in dumps older than the image infinite light
+                geom = np.ascontiguousarray(np.pad(geom, ((0, 0), (0, capi.LIGHT_GEOMETRY_FLOATS - geom.shape[1]))))
             keep.append(geom)
             r.light_geometry = geom.ctypes.data_as(C.POINTER(C.c_float))
         meshes = (capi.MeshAttr * max(nme, 1))()

@@ -393,10 +393,26 @@ def _gbuffer_film(out, xres, yres):
             '"bool saveVariance" true "bool saveRelativeVariance" true')
 
 
+def _envmap_lines(path, res):
+    """ImageInfiniteLight (lights.h:557-643): an equal-area square image written next to the scene as a PFM - a dim
+    bluish sky with two bright warm patches - turned so that the image's pole does not sit on a scene axis."""
+    g = (np.arange(res) + 0.5) / res
+    u, v = np.meshgrid(g, g)
+    img = np.stack([0.25 + 0.2 * v, 0.3 + 0.25 * u, 0.45 + 0.3 * u * v], axis=-1)
+    img += 40.0 * np.exp(-((u - 0.62) ** 2 + (v - 0.35) ** 2) / 0.004)[..., None] * np.array([1.0, 0.8, 0.5])
+    img += 12.0 * np.exp(-((u - 0.2) ** 2 + (v - 0.8) ** 2) / 0.01)[..., None] * np.array([0.9, 0.9, 1.0])
+    pfm = os.path.splitext(path)[0] + "_env.pfm"
+    with open(pfm, "wb") as f:  # PFM: rows bottom to top, little endian
+        f.write(f"PF\n{res} {res}\n-1.0\n".encode())
+        f.write(np.ascontiguousarray(img[::-1], "<f4").tobytes())
+    return ['AttributeBegin', '  Rotate 200 0 1 0', '  Rotate 65 1 0 0',
+            f'  LightSource "infinite" "string filename" "{pfm}" "float scale" 0.6', 'AttributeEnd']
+
+
 def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="cornell.pfm", seed=0,
                  boxes=(None, None), regularize=False, instanced=False, many_lights=0, infinite=None,
                  film="rgb", nbuckets=31, patches=False, smooth=False, alpha=False, lights=(), sampler="zsobol",
-                 pixelfilter="box"):
+                 pixelfilter="box", envmap=0):
     """BASELINE config 1 as a .pbrt file over cornell_box()'s geometry: diffuse walls (white / red / green),
     ceiling quad emitter `rgb L [17 12 4]`, perspective camera fov 39.3, rgb film, box filter, zsobol."""
     sc = cornell_box()
@@ -560,6 +576,8 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
                   '  ' + ball((0.15, 0.05, 0.2), 0.1, 8, 3, vmax=0.5 * np.pi, with_uv=False), 'AttributeEnd']
     if infinite is not None:
         lines.append(f'LightSource "infinite" "rgb L" [{infinite[0]} {infinite[1]} {infinite[2]}]')
+    if envmap:  # an image infinite light of envmap x envmap pixels; reaches the room through its open front
+        lines += _envmap_lines(path, int(envmap))
     with open(path, "w") as f:
         f.write("\n".join(lines) + "\n")
     return sc
@@ -900,7 +918,7 @@ def with_density_grid(d, density, medium=0):
 
 
 def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm", seed=0, grid=256, density=None,
-                 fog=True, crop=None, lightsampler="bvh", patch_cap=False, lights=(), sampler="zsobol"):
+                 fog=True, crop=None, lightsampler="bvh", patch_cap=False, lights=(), sampler="zsobol", envmap=0):
     """BASELINE configs[4]: VolPathIntegrator in the Cornell room: a thin homogeneous fog fills the room (an
     `interface` quad closes the open front; the camera stays in vacuum: a camera medium trips a race in the
     reference's BasicScene::GetMedium / CreateMedia, scene.cpp:809-850), and a box-shaped `interface` shell
@@ -952,6 +970,8 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
             lines.append(f'  Material "diffuse" "rgb reflectance" [{c[0]} {c[1]} {c[2]}]')
         lines.append('  ' + _mesh_pbrt(m))
         lines.append('AttributeEnd')
+    if envmap:  # seen through the front cap (an interface quad) by escaped rays and by light samples
+        lines += _envmap_lines(path, int(envmap))
     for name in lights:  # LIGHTS names or LightSource lines; inside the room, so in the fog
         lines += ['AttributeBegin', f'  MediumInterface {outside} {outside}', '  ' + LIGHTS.get(name, name), 'AttributeEnd']
     # the shell: interface material (no BSDF), cloud inside, fog (or vacuum) outside; slightly larger than

@@ -228,6 +228,12 @@ TIGHT_CASES = {
     "tight_coatcond": ("cornell", dict(res=32, spp=2048, maxdepth=5, boxes=("coated_conductor", "coated_conductor_rough"))),
     "tight_coatcond2": ("cornell", dict(res=32, spp=4096, maxdepth=5, boxes=("coated_conductor_both", "coated_conductor"),
                                         regularize=True)),
+    # ImageInfiniteLight: a 32 x 32 equal-area map lights the room through its open front, beside the ceiling
+    # emitter; under the BVH and the power light sampler (escaped rays weighted against the light's compensated pdf)
+    "tight_envmap": ("cornell", dict(res=32, spp=4096, maxdepth=5, lightsampler="bvh", envmap=32,
+                                     boxes=(None, "conductor_smooth"))),
+    "tight_envmap_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=8192, envmap=32)),
+    "tight_envmap_power": ("cornell", dict(res=32, spp=4096, maxdepth=4, lightsampler="power", envmap=32)),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),
 }

@@ -132,6 +132,8 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     rs.infiniteLights = rh.infiniteLights.data();
     rs.lightGeom = rh.lightGeom.empty() ? nullptr : rh.lightGeom.data();
     rs.film.filterTable = rh.filterTable.empty() ? nullptr : rh.filterTable.data();
+    rs.envImage = rh.envImage.data();
+    rs.envDist = rh.envDist.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
@@ -193,6 +195,8 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     rs.infiniteLights = rh.infiniteLights.data();
     rs.lightGeom = rh.lightGeom.empty() ? nullptr : rh.lightGeom.data();
     rs.film.filterTable = rh.filterTable.empty() ? nullptr : rh.filterTable.data();
+    rs.envImage = rh.envImage.data();
+    rs.envDist = rh.envDist.data();
     rs.prims = hs.prims.data();
     rs.instances = hs.instances.data();
     rs.camera.lens = rh.lens.data();
