@@ -317,6 +317,8 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("an image infinite light needs env_image, env_distribution and env_resolution");
             for (size_t k = 0; k < size_t(res) * res; ++k)
                 if (!std::isfinite(d->env_distribution[k]) || d->env_distribution[k] < 0) return bad("env_distribution must be finite and >= 0");
+            for (size_t k = 0; k < 4 * size_t(res) * res; ++k)
+                if (std::isnan(d->env_image[k])) return bad("env_image holds a NaN");  // (c2 = -inf is what a black pixel gets)
             out.rs.envLight = int32_t(i);
             out.rs.envRes = res;
             out.envImage.assign(d->env_image, d->env_image + 4 * size_t(res) * res);

@@ -335,6 +335,9 @@ B2_HD int EnvPixel(int res, float pu, float pv) {
         y = 2 * res - 1 - y;
     }
     if (res == 1) x = y = 0;
+    // (a non-finite direction must not index outside the image)
+    x = x < 0 ? 0 : (x > res - 1 ? res - 1 : x);
+    y = y < 0 ? 0 : (y > res - 1 ? res - 1 : y);
     return y * res + x;
 }
 // ImageLe (lights.h:626-633) at one wavelength: scale * RGBIlluminantSpectrum(rgb)(lambda) = scale * (s * S(poly(lambda))) *
