@@ -259,6 +259,10 @@ typedef struct b200pt_mesh_attr {
      * its corner_uv is ignored. */
     const float *corner_n;
     const float *corner_uv;
+    /* TriangleMesh::s, the per-vertex shading tangents (shapes.h:950-959), per corner like corner_n (3 x 3 floats per
+     * triangle), or NULL: the interpolated tangent replaces dpdu before it is made orthogonal to the shading normal.
+     * Triangle meshes only. */
+    const float *corner_s;
 } b200pt_mesh_attr;
 
 /* One participating medium with a Henyey-Greenstein phase function and no emission.

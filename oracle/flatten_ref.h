@@ -477,8 +477,8 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
     std::vector<uint32_t> nv, nt;
     std::vector<float> P;
     std::vector<int32_t> idx, patchIdx;
-    std::vector<uint32_t> meshKind, meshHasN, meshHasUV;
-    std::vector<float> cornerN, cornerUV;
+    std::vector<uint32_t> meshKind, meshHasN, meshHasUV, meshHasS;
+    std::vector<float> cornerN, cornerUV, cornerS;
     for (size_t m = 0; m < nMeshAll; ++m) {
         if (meshRemap[m] < 0) continue;
         if (m >= nTriMeshes) {
@@ -490,6 +490,7 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
             meshKind.push_back(1);
             meshHasN.push_back(mesh->n ? 1 : 0);  // four corner normals per patch
             meshHasUV.push_back(0);
+            meshHasS.push_back(0);
             for (int i = 0; mesh->n && i < 4 * mesh->nPatches; ++i) {
                 const Normal3f &vn = mesh->n[mesh->vertexIndices[i]];
                 cornerN.insert(cornerN.end(), {vn.x, vn.y, vn.z});
@@ -500,14 +501,15 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         }
         meshKind.push_back(0);
         const TriangleMesh *mesh = allMeshes[m];
-        if (mesh->s) die("per-vertex tangents (S) are not dumped");
         // per-vertex normals / uv leave as per-corner arrays (3 per triangle), so the device needs no index buffer
         meshHasN.push_back(mesh->n ? 1 : 0);
         meshHasUV.push_back(mesh->uv ? 1 : 0);
+        meshHasS.push_back(mesh->s ? 1 : 0);
         for (int i = 0; i < 3 * mesh->nTriangles; ++i) {
             int v = mesh->vertexIndices[i];
             if (mesh->n) cornerN.insert(cornerN.end(), {mesh->n[v].x, mesh->n[v].y, mesh->n[v].z});
             if (mesh->uv) cornerUV.insert(cornerUV.end(), {mesh->uv[v].x, mesh->uv[v].y});
+            if (mesh->s) cornerS.insert(cornerS.end(), {mesh->s[v].x, mesh->s[v].y, mesh->s[v].z});
         }
         nv.push_back(mesh->nVertices);
         nt.push_back(mesh->nTriangles);
@@ -518,6 +520,10 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
     w.u32("mesh_ntris", {uint32_t(nMesh)}, nt);
     w.f32("P", {uint32_t(P.size() / 3), 3}, P);
     w.i32("indices", {uint32_t(idx.size() / 3), 3}, idx);
+    if (!cornerS.empty()) {  // per-vertex tangents (TriangleMesh::s), per corner like the normals
+        w.u32("mesh_has_s", {uint32_t(nMesh)}, meshHasS);
+        w.f32("corner_s", {uint32_t(cornerS.size() / 3), 3}, cornerS);
+    }
     if (!cornerN.empty() || !cornerUV.empty()) {
         w.u32("mesh_has_n", {uint32_t(nMesh)}, meshHasN);
         w.u32("mesh_has_uv", {uint32_t(nMesh)}, meshHasUV);

@@ -252,16 +252,17 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
     m.attrs.resize(std::max<size_t>(1, nMesh));
     const uint32_t *hasN = T.has("mesh_has_n") ? T.at("mesh_has_n").u() : nullptr;
     const uint32_t *hasUV = T.has("mesh_has_uv") ? T.at("mesh_has_uv").u() : nullptr;
+    const uint32_t *hasS = T.has("mesh_has_s") ? T.at("mesh_has_s").u() : nullptr;
     const uint32_t *kind = T.has("mesh_kind") ? T.at("mesh_kind").u() : nullptr;
     const uint32_t *ntris = T.at("mesh_ntris").u();
-    size_t nAt = 0, uvAt = 0;
+    size_t nAt = 0, uvAt = 0, sAt = 0;
     for (size_t i = 0; i < nMesh; ++i) {
         const int32_t *a = ma.i() + 3 * i;
         b200pt_mesh_attr &A = m.attrs[i];
         A.material = a[0];
         A.light_first = a[1];
         A.flip_normal = uint32_t(std::max(a[2], 0));
-        A.corner_n = A.corner_uv = nullptr;
+        A.corner_n = A.corner_uv = A.corner_s = nullptr;
         if (hasN && hasN[i]) {
             const size_t per = (kind && kind[i] == 1) ? 4 : 3;
             A.corner_n = T.at("corner_n").f() + 3 * nAt;
@@ -270,6 +271,10 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         if (hasUV && hasUV[i]) {
             A.corner_uv = T.at("corner_uv").f() + 2 * uvAt;
             uvAt += 3 * size_t(ntris[i]);
+        }
+        if (hasS && hasS[i]) {
+            A.corner_s = T.at("corner_s").f() + 3 * sAt;
+            sAt += 3 * size_t(ntris[i]);
         }
     }
     r.n_spectra = uint32_t(sv.rows());

@@ -150,7 +150,8 @@ class Light(C.Structure):
 
 class MeshAttr(C.Structure):
     _fields_ = [("material", C.c_int32), ("light_first", C.c_int32), ("flip_normal", C.c_uint32),
-                ("corner_n", C.POINTER(C.c_float)), ("corner_uv", C.POINTER(C.c_float))]
+                ("corner_n", C.POINTER(C.c_float)), ("corner_uv", C.POINTER(C.c_float)),
+                ("corner_s", C.POINTER(C.c_float))]
 
 
 class Medium(C.Structure):

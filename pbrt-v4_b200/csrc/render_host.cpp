@@ -280,10 +280,10 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
             if (mi < -1 || mo < -1 || mi >= int32_t(d->n_media) || mo >= int32_t(d->n_media))
                 return bad("mesh medium index out of range");
         }
-        uint32_t nOff = kNoCornerAttr, uvOff = kNoCornerAttr;
-        if (m.corner_n || m.corner_uv) {
+        uint32_t nOff = kNoCornerAttr, uvOff = kNoCornerAttr, sOff = kNoCornerAttr;
+        if (m.corner_n || m.corner_uv || m.corner_s) {
             const bool patch = (meshKind[i] & 1) != 0;  // four corners per patch, normals only
-            if (out.cornerAttr.size() + 18 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
+            if (out.cornerAttr.size() + 27 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
             if (m.corner_n) {
                 nOff = uint32_t(out.cornerAttr.size());
                 out.cornerAttr.insert(out.cornerAttr.end(), m.corner_n, m.corner_n + (patch ? 12 : 9) * size_t(meshTris[i]));
@@ -292,8 +292,12 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 uvOff = uint32_t(out.cornerAttr.size());
                 out.cornerAttr.insert(out.cornerAttr.end(), m.corner_uv, m.corner_uv + 6 * size_t(meshTris[i]));
             }
+            if (m.corner_s && !patch) {
+                sOff = uint32_t(out.cornerAttr.size());
+                out.cornerAttr.insert(out.cornerAttr.end(), m.corner_s, m.corner_s + 9 * size_t(meshTris[i]));
+            }
         }
-        out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, nOff, mi, mo, uvOff, 0};
+        out.meshes[i] = MeshAttrDev{m.material, m.light_first, m.flip_normal, nOff, mi, mo, uvOff, sOff};
     }
     out.rs.geomExt = (hs.hasPatches || !out.cornerAttr.empty()) ? 1u : 0u;
     // ... or one of the less common shading features: the material variants, the independent sampler, delta lights

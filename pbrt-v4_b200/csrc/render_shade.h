@@ -43,22 +43,32 @@ struct SurfHit {
 // per-corner normals / uv of triangle `tri` of a mesh, null where the mesh has none (MeshAttrDev::nOff, uvOff)
 struct CornerAttr {
     const float *n, *uv;
+    const float *s = nullptr;  // shading tangents (triangle meshes)
 };
 B2_HD CornerAttr CornersOf(const RenderSceneDev &rs, const MeshAttrDev &mesh, uint32_t tri, uint32_t kind = 0) {
     CornerAttr c;  // a bilinear patch has four corners (normals only)
     c.n = mesh.nOff != kNoCornerAttr ? rs.cornerAttr + mesh.nOff + ((kind & 1) ? 12 : 9) * size_t(tri) : nullptr;
     c.uv = mesh.uvOff != kNoCornerAttr ? rs.cornerAttr + mesh.uvOff + 6 * size_t(tri) : nullptr;
+    c.s = (mesh.sOff != kNoCornerAttr && !(kind & 1)) ? rs.cornerAttr + mesh.sOff + 9 * size_t(tri) : nullptr;
     return c;
 }
 
 // The `if (mesh->n || mesh->s)` block of Triangle::InteractionFromIntersection (shapes.h:934-1005) without
 // per-vertex tangents: interpolated shading normal, tangent = dpdu made orthogonal to it, and
 // SetShadingGeometry(..., orientationIsAuthoritative = true) (interaction.h:194-211): the geometric normal follows ns.
-B2_HD_NOINLINE void TriangleShadingNormal(SurfHit &h, const float *cn, float b0, float b1, float b2, V3 dpdu) {
-    V3 n0 = mk(cn[0], cn[1], cn[2]), n1 = mk(cn[3], cn[4], cn[5]), n2 = mk(cn[6], cn[7], cn[8]);
-    V3 ns = b0 * n0 + b1 * n1 + b2 * n2;
-    ns = LengthSquared(ns) > 0 ? Normalize(ns) : h.n;
+// cn / cs: the corners' normals / tangents, either may be null (mesh->n, mesh->s; shapes.h:943-959)
+B2_HD_NOINLINE void TriangleShadingNormal(SurfHit &h, const float *cn, const float *cs, float b0, float b1, float b2, V3 dpdu) {
+    V3 ns = h.n;
+    if (cn) {
+        V3 n0 = mk(cn[0], cn[1], cn[2]), n1 = mk(cn[3], cn[4], cn[5]), n2 = mk(cn[6], cn[7], cn[8]);
+        ns = b0 * n0 + b1 * n1 + b2 * n2;
+        ns = LengthSquared(ns) > 0 ? Normalize(ns) : h.n;
+    }
     V3 ss = dpdu;
+    if (cs) {
+        ss = b0 * mk(cs[0], cs[1], cs[2]) + b1 * mk(cs[3], cs[4], cs[5]) + b2 * mk(cs[6], cs[7], cs[8]);
+        if (LengthSquared(ss) == 0) ss = dpdu;
+    }
     V3 ts = Cross(ns, ss);
     if (LengthSquared(ts) > 0)
         ss = Cross(ts, ns);
@@ -106,7 +116,7 @@ B2_HD SurfHit TriangleInteraction(const TriVerts &t, float b0, float b1, float b
     h.ns = n;
     h.dpdus = dpdu;
     h.wo = Normalize(wo);  // Interaction constructor (interaction.h:36-41)
-    if (ca.n) TriangleShadingNormal(h, ca.n, b0, b1, b2, dpdu);
+    if (ca.n || ca.s) TriangleShadingNormal(h, ca.n, ca.s, b0, b1, b2, dpdu);
     return h;
 }
 

@@ -60,7 +60,7 @@ struct MeshAttrDev {
     uint32_t nOff;  // per-corner normals of triangle t at cornerAttr[nOff + 9 t], kNoCornerAttr = none
     int32_t mediumInside, mediumOutside;  // MediumInterface; equal = no transition (the ray keeps its medium)
     uint32_t uvOff;  // per-corner uv of triangle t at cornerAttr[uvOff + 6 t], kNoCornerAttr = none
-    uint32_t pad;
+    uint32_t sOff;   // per-corner shading tangents of triangle t at cornerAttr[sOff + 9 t], kNoCornerAttr = none
 };
 constexpr uint32_t kNoCornerAttr = 0xFFFFFFFFu;
 

@@ -153,8 +153,9 @@ class RenderScene:
         # per-corner normals / uv: the meshes that have them take their 3 * ntris rows from corner_n / corner_uv in order
         has_n = d["mesh_has_n"] if "mesh_has_n" in d else np.zeros(nme, np.uint32)
         has_uv = d["mesh_has_uv"] if "mesh_has_uv" in d else np.zeros(nme, np.uint32)
+        has_s = d["mesh_has_s"] if "mesh_has_s" in d else np.zeros(nme, np.uint32)
         ntris = d["mesh_ntris"].astype(np.int64)
-        n_at = uv_at = 0
+        n_at = uv_at = s_at = 0
         for i in range(nme):
             a = d["mesh_attr"][i]
             meshes[i] = capi.MeshAttr(int(a[0]), int(a[1]), int(max(a[2], 0)))
@@ -169,6 +170,11 @@ class RenderScene:
                 uv_at += 3 * int(ntris[i])
                 meshes[i].corner_uv = capi.fptr(cuv)
                 keep.append(cuv)
+            if has_s[i]:  # per-vertex shading tangents
+                cs = np.ascontiguousarray(d["corner_s"][s_at:s_at + 3 * ntris[i]], np.float32)
+                s_at += 3 * int(ntris[i])
+                meshes[i].corner_s = capi.fptr(cs)
+                keep.append(cs)
         r.n_spectra, r.n_materials, r.n_lights, r.n_meshes = ns, nm, nl, nme
         r.spectra, r.materials, r.lights, r.meshes = spectra, mats, lights, meshes
         keep += [spectra, mats, lights, meshes]

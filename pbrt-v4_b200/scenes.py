@@ -534,7 +534,7 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
         # triangle meshes with per-vertex normals and uv (Triangle::InteractionFromIntersection's shading geometry,
         # shapes.h:934-1005): an anisotropic metal ball, a diffuse ball with normals only, and a small emissive
         # dome whose normals decide its emitting side (Triangle::Sample's FaceForward(n, ns), shapes.h:1024-1029)
-        def ball(c, r, nu, nv, vmax=np.pi, with_uv=True, inward=False):
+        def ball(c, r, nu, nv, vmax=np.pi, with_uv=True, inward=False, with_n=True, tangents=None):
             th = np.linspace(0.0, vmax, nv + 1)
             ph = np.linspace(0.0, 2 * np.pi, nu + 1)
             nrm = np.array([[np.sin(t) * np.cos(f), np.cos(t), np.sin(t) * np.sin(f)] for t in th for f in ph])
@@ -551,8 +551,14 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
             if inward:
                 nrm = -nrm
             txt = (f'Shape "trianglemesh" "integer indices" [{" ".join(map(str, idx))}] "point3 P" '
-                   f'[{" ".join(f"{float(x):.7g}" for x in pts.reshape(-1))}] "normal N" '
-                   f'[{" ".join(f"{float(x):.7g}" for x in nrm.reshape(-1))}]')
+                   f'[{" ".join(f"{float(x):.7g}" for x in pts.reshape(-1))}]')
+            if with_n:
+                txt += f' "normal N" [{" ".join(f"{float(x):.7g}" for x in nrm.reshape(-1))}]'
+            if tangents is not None:
+                # per-vertex shading tangents (TriangleMesh::s, shapes.h:950-959): a swirl about `tangents`, an axis that
+                # is not the sphere's own; zero at the two vertices where the axis pierces it (falls back to dpdu)
+                sv = np.cross(nrm, np.asarray(tangents, float) / np.linalg.norm(tangents))
+                txt += f' "vector3 S" [{" ".join(f"{float(x):.7g}" for x in sv.reshape(-1))}]'
             if with_uv:
                 txt += f' "point2 uv" [{" ".join(f"{float(x):.7g}" for x in uv.reshape(-1))}]'
             return txt
@@ -565,6 +571,13 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
                       '  ObjectInstance "ball"', 'AttributeEnd',
                       'AttributeBegin', '  Translate 0.3 0.25 0.2', '  Rotate -20 1 0 0.4', '  Scale 0.08 0.1 0.08',
                       '  ObjectInstance "ball"', 'AttributeEnd']
+        elif smooth == "tangents":
+            # the anisotropic metal ball with normals, uv AND tangents; a second, flat-shaded one with tangents only
+            lines += ['AttributeBegin', '  ' + MATERIALS["conductor_reflectance"],
+                      '  ' + ball((0.68, 0.5, 0.3), 0.16, 12, 8, tangents=(0.3, 0.2, 1.0)), 'AttributeEnd',
+                      'AttributeBegin', '  ' + MATERIALS["conductor_reflectance"],
+                      '  ' + ball((0.3, 0.3, 0.25), 0.12, 10, 6, with_uv=False, with_n=False, tangents=(1.0, 0.4, 0.1)),
+                      'AttributeEnd']
         else:
             lines += ['AttributeBegin', '  ' + MATERIALS["conductor_reflectance"], '  ' + ball((0.68, 0.5, 0.3), 0.16, 12, 8),
                       'AttributeEnd']

@@ -79,6 +79,8 @@ RENDER_CASES = {
     # per-vertex normals and uv on triangle meshes (shading geometry; an emissive dome oriented by its normals)
     "cornell_smooth_r64_s16": dict(res=64, spp=16, maxdepth=5, smooth=True),
     "cornell_smoothinst_r64_s16": dict(res=64, spp=16, maxdepth=5, smooth="instanced"),
+    # per-vertex shading tangents (TriangleMesh::s) under anisotropic metal: with normals and uv, and on their own
+    "cornell_tangents_r64_s16": dict(res=64, spp=16, maxdepth=5, smooth="tangents"),
     # alpha cut-outs (constant alpha 0.5 / 0.3 / 0): the test runs inside traversal, for path and shadow rays alike
     "cornell_alpha_r64_s16": dict(res=64, spp=16, maxdepth=5, alpha=True),
     # vertex normals on bilinear patches: shading geometry of a wavy sheet, an emitter oriented by its normals
