@@ -443,6 +443,12 @@ int b200pt_film_clear(b200pt_render *r);
  * reduction that only needs R G B + Radiance can stop after the first 4 + 31 planes) */
 int b200pt_film_device_ptr(b200pt_render *r, void **ptr, uint64_t *n_doubles);
 int b200pt_film_read(b200pt_render *r, double *rgb_weight);
+/* Multi-GPU hand-back without the host touching the buffer: ncclReduce (double, sum, in place) of the first
+ * n_doubles doubles of this rank's film (0 = all of it) to rank `root` of `nccl_comm` - an ncclComm_t the host made,
+ * one rank per render object - on the context's stream; afterwards root's film holds the frame (every rank rendered
+ * its stripe of sample indices, b200pt_render_run).  The NCCL the process has already loaded is used (dlopen; the
+ * library does not link it).  The reference has no counterpart: its film lives in one address space. */
+int b200pt_film_reduce(b200pt_render *r, void *nccl_comm, int32_t root, uint64_t n_doubles);
 /* spectral film only: the S0.* channels of SpectralFilm::GetImage (film.cpp:1221-1273), n_buckets floats per
  * pixel (bucketSums / weightSums, 0 where no weight). */
 int b200pt_film_spectral_image(b200pt_render *r, float *buckets);

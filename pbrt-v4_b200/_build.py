@@ -83,7 +83,7 @@ def build(verbose=False, force=False):
         with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
             list(ex.map(lambda c: _run(c, verbose), jobs))
     if force or jobs or any(_newer(o, LIB, []) for o in objs):
-        _run([NVCC, "-shared", "-o", LIB] + objs + GENCODE + ["-cudart", "static"], verbose)
+        _run([NVCC, "-shared", "-o", LIB] + objs + GENCODE + ["-cudart", "static", "-ldl"], verbose)
     return LIB
 
 

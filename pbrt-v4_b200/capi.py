@@ -208,6 +208,7 @@ SYMBOLS.update({
     "b200pt_render_run": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
     "b200pt_film_clear": (C.c_int, [C.c_void_p]),
     "b200pt_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
+    "b200pt_film_reduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64]),
     "b200pt_film_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "b200pt_film_image": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "b200pt_film_write_exr": (C.c_int, [C.c_void_p, C.c_uint32, C.c_char_p, C.c_int32]),

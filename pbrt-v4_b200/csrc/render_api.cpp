@@ -2,6 +2,9 @@
 // loop that strings the kernels together (the role of WavefrontPathIntegrator::Render,
 // wavefront/integrator.cpp:290-493), film read-out.  Host code only; no CPU rendering path exists.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <mutex>
 
 #include <algorithm>
 #include <cstdlib>
@@ -348,6 +351,38 @@ int b200pt_film_device_ptr(b200pt_render *r, void **ptr, uint64_t *n_doubles) {
     if (!r || !ptr) return B200PT_ERR_INVALID;
     *ptr = r->dFilm;
     if (n_doubles) *n_doubles = r->filmDoubles;
+    return B200PT_OK;
+}
+
+// ncclReduce out of the NCCL the process already has (the host made `comm` with it), else out of libnccl.so.2: the
+// library itself does not link NCCL, a single-GPU host never needs it.
+int b200pt_film_reduce(b200pt_render *r, void *nccl_comm, int32_t root, uint64_t n_doubles) {
+    if (!r || !nccl_comm || root < 0) return B200PT_ERR_INVALID;
+    b200pt_ctx *ctx = r->scene->ctx;
+    if (n_doubles == 0 || n_doubles > r->filmDoubles) n_doubles = r->filmDoubles;
+    using ReduceFn = int (*)(const void *, void *, size_t, int, int, int, void *, cudaStream_t);
+    static ReduceFn reduce = nullptr;
+    static std::mutex mu;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!reduce) {
+            void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+            if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+            if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+            reduce = h ? reinterpret_cast<ReduceFn>(dlsym(h, "ncclReduce")) : nullptr;
+            if (!reduce) {
+                ctx->err = "b200pt_film_reduce: no NCCL in this process and libnccl.so.2 cannot be loaded";
+                return B200PT_ERR_INVALID;
+            }
+        }
+    }
+    B2_CUDA(ctx, cudaSetDevice(ctx->device));
+    // ncclReduce(send, recv, count, ncclFloat64 = 8, ncclSum = 0, root, comm, stream), in place on the film buffer
+    int rc = reduce(r->dFilm, r->dFilm, size_t(n_doubles), 8, 0, root, nccl_comm, ctx->stream);
+    if (rc != 0) {
+        ctx->err = "b200pt_film_reduce: ncclReduce returned " + std::to_string(rc);
+        return B200PT_ERR_CUDA;
+    }
     return B200PT_OK;
 }
 

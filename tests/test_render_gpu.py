@@ -303,6 +303,36 @@ def test_filter_sampler_filters(P, name):
     assert rrmse(img, ref) <= 1e-3, rrmse(img, ref)
 
 
+def test_film_reduce_single_rank(P):
+    """b200pt_film_reduce (the C ABI's ncclReduce of the film; scripts/film_reduce_check.py runs it over N GPUs and
+    compares with one GPU's frame: profiles/r02_film_reduce_n2.log).  Here on one GPU: a communicator of one rank, made
+    through ctypes as a C++ host would; the call must succeed on the NCCL torch has loaded and leave the film as it is."""
+    import ctypes as C
+    import torch
+    torch.zeros(1, device="cuda")
+    nccl = C.CDLL("libnccl.so.2", mode=C.RTLD_GLOBAL)
+
+    class UniqueId(C.Structure):
+        _fields_ = [("internal", C.c_char * 128)]
+    uid, comm = UniqueId(), C.c_void_p()
+    assert nccl.ncclGetUniqueId(C.byref(uid)) == 0
+    nccl.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, UniqueId, C.c_int]
+    assert nccl.ncclCommInitRank(C.byref(comm), 1, uid, 0) == 0
+    rsc = P.RenderScene.load(os.path.join(GOLD, "cornell_spectral_r48_s16.b2rs"))
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        before = [a.copy() for a in r.film_all() if a is not None]
+        P.capi.check(P.capi.lib().b200pt_film_reduce(r._r, comm, 0, 0), r.agg._ctx)
+        r.agg.sync()
+        after = [a for a in r.film_all() if a is not None]
+        assert all(np.array_equal(a, b) for a, b in zip(before, after))
+        assert P.capi.lib().b200pt_film_reduce(r._r, None, 0, 0) == P.capi.ERR_INVALID
+    finally:
+        r.close()
+        nccl.ncclCommDestroy(comm)
+
+
 def test_gbuffer_film_matches_reference(P):
     """GBufferFilm, the ISET spectral film (film.cpp:597-666, 743-1044): every channel of the
     reference's Film::GetImage - R G B, Radiance.C01-31, P, MaterialId, InstanceId, Ns, N, Variance, RelativeVariance -
