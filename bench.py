@@ -228,9 +228,11 @@ def render_cpu_reference(args, P, local, stream):
         pbrt, pfm = os.path.join(tmp, "c.pbrt"), os.path.join(tmp, "c.pfm")
         P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
         ref, secs = refrun.render(pbrt, pfm)
-        tables = P.scenes.load_b2rs(refrun.dump_scene(pbrt, os.path.join(tmp, "c.b2rs")))
-    parity = image_parity(gpu_image_of_tables(P, tables, local, stream), ref)
-    parity["sample"] = f"{kw['res']}x{kw['res']}, {kw['spp']} spp, same sampler seed"
+        tables = P.scenes.load_b2rs(refrun.dump_scene(pbrt, os.path.join(tmp, "c.b2rs"))) if local is not None else None
+    parity = None  # (--impl reference: the reference alone, no GPU in that process)
+    if local is not None:
+        parity = image_parity(gpu_image_of_tables(P, tables, local, stream), ref)
+        parity["sample"] = f"{kw['res']}x{kw['res']}, {kw['spp']} spp, same sampler seed"
     n = kw["res"] * kw["res"] * kw["spp"]
     return {"value": n / secs * 1e-6, "parity": parity, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
             "seconds": secs,
@@ -743,7 +745,7 @@ def run_reference(args, rank, world):
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     if not args.no_render:
-        rc = render_cpu_reference(args, P)
+        rc = render_cpu_reference(args, P, None, None)
         line["render"] = {"metric": "render_msamples_per_s", "unit": "Msamples/s", "value": rc["value"],
                           "cpu_baseline": rc}
     print(json.dumps(line), flush=True)
