@@ -303,6 +303,26 @@ def test_filter_sampler_filters(P, name):
     assert rrmse(img, ref) <= 1e-3, rrmse(img, ref)
 
 
+@pytest.mark.parametrize("case,drop,message", [
+    ("tight_lights", "lights_geom", "light_geometry"),            # delta lights without their placement
+    ("tight_gaussian", "filter_table", "filter_table"),           # a FilterSampler filter without its table
+    ("tight_envmap", "env_image", "env_image"),                   # an image infinite light without its image
+    ("tight_independent", "sampler:7", "sampler"),                # a sampler the library has not got
+])
+def test_render_create_refuses_incomplete_descriptions(P, case, drop, message):
+    """The round-2 inputs are refused with B200PT_ERR_INVALID and a message that names the field, not rendered wrongly
+    (the reference aborts in the corresponding Create functions)."""
+    rsc = P.RenderScene.load(os.path.join(GOLD, case + ".b2rs"))
+    if drop.startswith("sampler:"):
+        rsc.d["sampler"] = rsc.d["sampler"].copy()
+        rsc.d["sampler"][0] = int(drop.split(":")[1])
+    else:
+        del rsc.d[drop]
+    with pytest.raises(P.capi.B200PTError) as e:
+        P.B200Renderer(rsc).close()
+    assert message in str(e.value), str(e.value)
+
+
 def test_film_reduce_single_rank(P):
     """b200pt_film_reduce (the C ABI's ncclReduce of the film; scripts/film_reduce_check.py runs it over N GPUs and
     compares with one GPU's frame: profiles/r02_film_reduce_n2.log).  Here on one GPU: a communicator of one rank, made
