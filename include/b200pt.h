@@ -388,7 +388,8 @@ typedef struct b200pt_render_desc {
      * LanczosSinc; filters.h:80-230, filters.cpp:92-118) need filter_table: the host's tabulation of Filter::Evaluate
      * at the centres of filter_table_size[0] x filter_table_size[1] cells over [-radius, radius]^2, row-major with x
      * fastest (FilterSampler::f: int(32 * radius) cells per axis) - the sampling distribution is built from it as
-     * the reference builds its PiecewiseConstant2D.  B200PT_FILTER_TRIANGLE (its own analytic Sample) is refused. */
+     * the reference builds its PiecewiseConstant2D.  B200PT_FILTER_TRIANGLE (TriangleFilter, filters.h:204-239) samples its
+     * tent analytically (SampleTent), weight 1, and needs no table. */
     uint32_t filter_type;
     /* placement of the delta lights, B200PT_LIGHT_GEOMETRY_FLOATS floats per light for ALL n_lights lights (rows of
      * other light types are ignored); NULL when the scene has none.  Row: [0..2] point / spot: renderFromLight(0,0,0)

@@ -232,7 +232,7 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
     auto dumpFilm = [&](const auto *rf) {
         Bounds2i pb = rf->pixelBounds;
         w.i32("film_ints", {6}, {pb.pMin.x, pb.pMin.y, pb.pMax.x, pb.pMax.y, rf->fullResolution.x, rf->fullResolution.y});
-        // filter_type as include/b200pt.h numbers them; the library refuses what it has not got (box only)
+        // filter_type as include/b200pt.h numbers them (4 = triangle)
         const uint32_t ft = rf->filter.template Is<BoxFilter>() ? 0u : rf->filter.template Is<GaussianFilter>() ? 1u
                           : rf->filter.template Is<MitchellFilter>() ? 2u : rf->filter.template Is<LanczosSincFilter>() ? 3u : 4u;
         w.u32("filter_type", {1}, {ft});

@@ -226,10 +226,24 @@ B2_HD float Piecewise2DPDF(const float *f, int nx, int ny, float px, float py) {
 
 // Filter::Sample(u): BoxFilter (filters.h:60-64), or FilterSampler::Sample (filters.h:27-33): the point from the
 // tabulated distribution (PiecewiseConstant2D::Sample, util/sampling.h:752-762), weight f[cell] / pdf
+// SampleTent (util/sampling.h:196-201): SampleDiscrete({0.5, 0.5}, u, nullptr, &u) picks the half, SampleLinear the point
+B2_HD float SampleTent(float u, float r) {
+    float up = u;  // u * sumWeights, sumWeights = 1
+    if (up == 1.f) up = NextDown(up);
+    const bool upper = 0.5f <= up;
+    float ur = fminf((up - (upper ? 0.5f : 0.f)) / 0.5f, kOneMinusEps);
+    return upper ? r * SampleLinear(ur, 1, 0) : -r + r * SampleLinear(ur, 0, 1);
+}
 B2_HD void SampleFilter(const FilmDev &film, float u0, float u1, float &fx, float &fy, float &weight) {
     if (film.filterType == 0) {
         fx = Lerp(u0, -film.filterRadiusX, film.filterRadiusX);
         fy = Lerp(u1, -film.filterRadiusY, film.filterRadiusY);
+        weight = 1.f;
+        return;
+    }
+    if (film.filterType == 4) {  // TriangleFilter::Sample (filters.h:224-227): tent-distributed, weight 1
+        fx = SampleTent(u0, film.filterRadiusX);
+        fy = SampleTent(u1, film.filterRadiusY);
         weight = 1.f;
         return;
     }

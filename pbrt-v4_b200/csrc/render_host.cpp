@@ -60,9 +60,9 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 return bad("omni camera: microlens simulation radius must be 0..8");
         }
     }
-    if (d->filter_type == B200PT_FILTER_TRIANGLE || d->filter_type > B200PT_FILTER_SINC)
-        return bad("unsupported pixel filter: box, and gaussian / mitchell / sinc through filter_table, are implemented");
-    if (d->filter_type != B200PT_FILTER_BOX) {
+    if (d->filter_type > B200PT_FILTER_TRIANGLE)
+        return bad("unsupported pixel filter: box, triangle, and gaussian / mitchell / sinc through filter_table, are implemented");
+    if (d->filter_type != B200PT_FILTER_BOX && d->filter_type != B200PT_FILTER_TRIANGLE) {
         const int nx = d->filter_table_size[0], ny = d->filter_table_size[1];
         if (!d->filter_table || nx < 1 || ny < 1 || nx > 4096 || ny > 4096)
             return bad("filter_type needs filter_table (the tabulated filter function) and its size");
@@ -153,8 +153,9 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     rs.film.fullResX = d->full_resolution[0];
     rs.film.fullResY = d->full_resolution[1];
     rs.film.filterType = d->filter_type;
-    rs.film.filterNx = d->filter_type ? d->filter_table_size[0] : 0;
-    rs.film.filterNy = d->filter_type ? d->filter_table_size[1] : 0;
+    const bool tabulated = d->filter_type != B200PT_FILTER_BOX && d->filter_type != B200PT_FILTER_TRIANGLE;
+    rs.film.filterNx = tabulated ? d->filter_table_size[0] : 0;
+    rs.film.filterNy = tabulated ? d->filter_table_size[1] : 0;
     rs.film.filterTable = nullptr;  // filled by the owner of the storage
     rs.film.filterRadiusX = d->filter_radius[0];
     rs.film.filterRadiusY = d->filter_radius[1];

@@ -224,6 +224,7 @@ TIGHT_CASES = {
     # (negative lobes: negative sample weights), and a Lanczos sinc with unequal radii; 1024 spp on a 24 x 24 frame
     "tight_gaussian": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter="gaussian")),
     "tight_mitchell": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter='"mitchell" "float B" 0.2 "float C" 0.4')),
+    "tight_triangle": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter='"triangle" "float xradius" 2 "float yradius" 1.5')),
     "tight_sinc": ("cornell", dict(res=24, spp=1024, maxdepth=4, pixelfilter='"sinc" "float xradius" 3 "float yradius" 2.5')),
     # CoatedConductorMaterial: smooth coat over rough copper + rough coat over a smooth base; and both rough
     # with a dispersive coat (TerminateSecondary)

@@ -229,7 +229,7 @@ def test_golden_image_config5_volpath(P, rendercheck, name):
     assert abs(img.mean() - ref.mean()) <= TOL_MEAN * ref.mean()
 
 
-@pytest.mark.parametrize("name", ["tight_gaussian", "tight_mitchell", "tight_sinc"])
+@pytest.mark.parametrize("name", ["tight_gaussian", "tight_mitchell", "tight_sinc", "tight_triangle"])
 def test_filter_sampler_filters(P, rendercheck, name):
     """The FilterSampler filters (Gaussian, Mitchell, Lanczos sinc; filters.cpp:92-118) through the host loop over the
     kernels' headers: the reference's paths and weights, image within rRMSE 1e-4."""
