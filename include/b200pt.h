@@ -410,6 +410,15 @@ typedef struct b200pt_render_desc {
     const float *env_image;
     const float *env_distribution;
     int32_t env_resolution;
+    /* GBufferFilm's Albedo.R G B (film.cpp:640-644, 846-858): with gbuffer_albedo != 0 the first visible surface's
+     * albedo is estimated as the reference does (bsdf.rho over its 16 fixed sample points, cpu/integrators.cpp:690-711)
+     * and summed as (albedo * illuminant).ToRGB(lambda, colorSpace): gbuffer_xyz_spectrum = Spectra::X / Y / Z,
+     * gbuffer_illuminant = the film colour space's illuminant (both indices into `spectra`), gbuffer_rgb_from_xyz =
+     * its RGBFromXYZ, row major.  Costs 16 BSDF samples per camera ray; leave 0 when the film does not save albedo. */
+    uint32_t gbuffer_albedo;
+    int32_t gbuffer_xyz_spectrum[3];
+    int32_t gbuffer_illuminant;
+    float gbuffer_rgb_from_xyz[9];
 } b200pt_render_desc;
 #define B200PT_LIGHT_GEOMETRY_FLOATS 24
 enum { B200PT_SAMPLER_ZSOBOL = 0, B200PT_SAMPLER_INDEPENDENT = 1 };
@@ -457,13 +466,14 @@ int b200pt_film_spectral_image(b200pt_render *r, float *buckets);
 int b200pt_film_image(b200pt_render *r, float *rgb);
 /* GBufferFilm::GetImage (film.cpp:743-1044) for film_type 2: R, G, B and, in the reference's channel order, the groups
  * selected in `channels` (the film's save* switches, film.cpp:1062-1073): Radiance.C01-31 (bucket sum / sum of all sample
- * weights: the CPU build's observed behaviour), P.X-Z, MaterialId, InstanceId, Ns.X-Z, N.X-Z,
+ * weights: the CPU build's observed behaviour), Albedo.R-B (rgbAlbedoSum / rgbWeightSum), P.X-Z, MaterialId, InstanceId, Ns.X-Z, N.X-Z,
  * Variance.R-B, RelativeVariance.R-B.  out: height x width x (*n_channels) floats, channels last; out == NULL only
  * reports *n_channels.  Under multi-GPU rendering the sums reduce with the film buffer; the two id channels are this
  * rank's (the reference keeps the last sample's). */
 enum {
     B200PT_GBUFFER_RADIANCE = 1, B200PT_GBUFFER_POSITION = 2, B200PT_GBUFFER_MATERIAL = 4, B200PT_GBUFFER_INSTANCE = 8,
-    B200PT_GBUFFER_NS = 16, B200PT_GBUFFER_NORMAL = 32, B200PT_GBUFFER_VARIANCE = 64, B200PT_GBUFFER_RELATIVE_VARIANCE = 128
+    B200PT_GBUFFER_NS = 16, B200PT_GBUFFER_NORMAL = 32, B200PT_GBUFFER_VARIANCE = 64, B200PT_GBUFFER_RELATIVE_VARIANCE = 128,
+    B200PT_GBUFFER_ALBEDO = 256 /* Albedo.R G B, between Radiance and P in the channel order; needs gbuffer_albedo */
 };
 int b200pt_film_gbuffer_image(b200pt_render *r, uint32_t channels, float *out, int32_t *n_channels);
 /* Film::WriteImage for the .exr case (film.cpp:542-574 -> Image::WriteEXR, util/image.cpp:1008+): the film's image

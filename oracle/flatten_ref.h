@@ -277,6 +277,13 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         }
         w.f32("gbuffer_from_render", {16}, m);
         w.f32("gbuffer_from_render_inv", {16}, mi);
+        if (gf->writeAlbedo) {  // Albedo.*: what (albedo * illuminant).ToRGB(lambda, colorSpace) needs (film.cpp:640-644)
+            w.i32("gbuffer_albedo", {4}, {pool.add(&Spectra::X(), 0), pool.add(&Spectra::Y(), 0), pool.add(&Spectra::Z(), 0),
+                                          pool.add(&gf->colorSpace->illuminant, 0)});
+            std::vector<float> rx(9);
+            for (int i = 0; i < 9; ++i) rx[i] = gf->colorSpace->RGBFromXYZ[i / 3][i % 3];
+            w.f32("gbuffer_rgb_from_xyz", {9}, rx);
+        }
     } else
         die("only the rgb, spectral and gbuffer films are dumped so far");
 

@@ -173,6 +173,13 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         memcpy(r.gbuffer_output_from_render, T.at("gbuffer_from_render").f(), 64);
         memcpy(r.gbuffer_output_from_render_inv, T.at("gbuffer_from_render_inv").f(), 64);
         r.material_ids = T.at("material_ids").i();
+        if (T.has("gbuffer_albedo")) {
+            const int32_t *ga = T.at("gbuffer_albedo").i();
+            r.gbuffer_albedo = 1;
+            memcpy(r.gbuffer_xyz_spectrum, ga, 12);
+            r.gbuffer_illuminant = ga[3];
+            memcpy(r.gbuffer_rgb_from_xyz, T.at("gbuffer_rgb_from_xyz").f(), 36);
+        }
     }
     if (r.film_type == 1 || r.film_type == 2) {
         const float *fs = T.at("film_spectral").f();
@@ -349,8 +356,9 @@ static void RenderB200(BasicScene &scene, int device, bool hostBvh) {
         // GBufferFilm writes EXR only (film.cpp:1081-1083) and the oracle build of the reference has no EXR writer
         // (oracle/ref.mk): the library's own - image finalised and packed on the device - writes the file, with the
         // channel groups the film's save* switches ask for.  (Albedo, dzdx / dzdy and the SVD basis are not built.)
-        if (gf->writeAlbedo || gf->writeDz || gf->writeBasis) die("pbrt_b200: saveAlbedo / saveDz / saveRadianceAsBasis are not built");
+        if (gf->writeDz || gf->writeBasis) die("pbrt_b200: saveDz / saveRadianceAsBasis are not built");
         uint32_t ch = (gf->writeRadiance ? B200PT_GBUFFER_RADIANCE : 0) | (gf->writePosition ? B200PT_GBUFFER_POSITION : 0) |
+                      (gf->writeAlbedo ? B200PT_GBUFFER_ALBEDO : 0) |
                       (gf->writeMaterial ? B200PT_GBUFFER_MATERIAL : 0) | (gf->writeInstance ? B200PT_GBUFFER_INSTANCE : 0) |
                       (gf->writeNs ? B200PT_GBUFFER_NS : 0) | (gf->writeNormal ? B200PT_GBUFFER_NORMAL : 0) |
                       (gf->writeVariance ? B200PT_GBUFFER_VARIANCE : 0) |

@@ -189,11 +189,14 @@ class RenderDesc(C.Structure):
                 ("material_ids", C.POINTER(C.c_int32)), ("filter_type", C.c_uint32),
                 ("light_geometry", C.POINTER(C.c_float)),
                 ("filter_table", C.POINTER(C.c_float)), ("filter_table_size", C.c_int32 * 2),
-                ("env_image", C.POINTER(C.c_float)), ("env_distribution", C.POINTER(C.c_float)), ("env_resolution", C.c_int32)]
+                ("env_image", C.POINTER(C.c_float)), ("env_distribution", C.POINTER(C.c_float)), ("env_resolution", C.c_int32),
+                ("gbuffer_albedo", C.c_uint32), ("gbuffer_xyz_spectrum", C.c_int32 * 3), ("gbuffer_illuminant", C.c_int32),
+                ("gbuffer_rgb_from_xyz", C.c_float * 9)]
 
 
 GBUFFER_RADIANCE, GBUFFER_POSITION, GBUFFER_MATERIAL, GBUFFER_INSTANCE = 1, 2, 4, 8
 GBUFFER_NS, GBUFFER_NORMAL, GBUFFER_VARIANCE, GBUFFER_RELATIVE_VARIANCE = 16, 32, 64, 128
+GBUFFER_ALBEDO = 256
 
 
 class RenderStats(C.Structure):

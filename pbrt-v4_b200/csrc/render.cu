@@ -171,6 +171,14 @@ struct DevIO {
         a[10 * N] = (float)material;
         a[11 * N] = (float)instance;
     }
+    // the surface's albedo as XYZ, under the wavelength pdf of a path that keeps all its wavelengths [0..2] and of one
+    // that ends with the secondary ones terminated [3..5]: the film converts with the lambda the path ENDS with
+    __device__ __forceinline__ bool WantsAlbedo() const { return pb.aov != nullptr; }
+    __device__ __forceinline__ void VisibleSurfaceAlbedo(const float xyz[6]) {
+        float *a = pb.aov + path;
+        const long long N = pb.n;
+        for (int i = 0; i < 6; ++i) a[(12 + i) * N] = xyz[i];
+    }
     __device__ __forceinline__ void ShadowBegin() { slot = QueuePush(nShadow); }
     __device__ __forceinline__ void SetLd(int k, float v) { pb.Ld[(long long)k * pb.n + slot] = v; }
     __device__ __forceinline__ void ShadowEnd(bool valid, V3 o, V3 d, float tMax) {
@@ -204,6 +212,8 @@ struct GlobalIO {
     int slot;
     __device__ GlobalIO(const PassBuffers &b, int pathId, int *shadowCount) : pb(b), path(pathId), nShadow(shadowCount), slot(-1) {}
     __device__ __forceinline__ void VisibleSurface(V3, V3, V3, int, int) {}
+    __device__ __forceinline__ bool WantsAlbedo() const { return false; }
+    __device__ __forceinline__ void VisibleSurfaceAlbedo(const float *) {}
     __device__ __forceinline__ float Beta(int k) const { return pb.beta[(long long)k * pb.n + path]; }
     __device__ __forceinline__ void SetBeta(int k, float v) { pb.beta[(long long)k * pb.n + path] = v; }
     __device__ __forceinline__ float Ru(int k) const { return pb.ru[(long long)k * pb.n + path]; }
@@ -744,6 +754,14 @@ __global__ void FilmAddGBufferKernel(FilmDev fd, PassBuffers pb, int nPixels, in
                 acc[13 + c] += double(rgb[c]) * rgb[c];
             }
             acc[16] += 1;
+            if (fd.gbufferAlbedo) {  // rgbAlbedoSum += weight * (albedo * illuminant).ToRGB(lambda, colorSpace) (film.cpp:640-644)
+                const float *x = a + (((uint32_t)pb.ints[3 * n + path] & PF_TERMINATED_SECONDARY) ? 15 : 12) * n;
+                const float X = x[0], Y = x[n], Z = x[2 * n];
+                const float *m = fd.rgbFromXYZ;
+                acc[17] += w * (m[0] * X + m[1] * Y + m[2] * Z);
+                acc[18] += w * (m[3] * X + m[4] * Y + m[5] * Z);
+                acc[19] += w * (m[6] * X + m[7] * Y + m[8] * Z);
+            }
         }
         // p.materialId = visibleSurface->materialId: every sample writes it.  A sample without a VisibleSurface (no camera
         // ray through the lens, an escaped ray) hands the film a default-constructed one whose ids are never initialised
@@ -784,6 +802,11 @@ __global__ void FilmGBufferImageKernel(FilmDev film, const double *acc, const fl
         }
     const double *gq = acc + (4ll + film.nBuckets) * P + pix;
     const float gw = (float)gq[0];
+    if (channels & B200PT_GBUFFER_ALBEDO)  // albedoRgb / rgbWeightSum, as it is (film.cpp:846-858, 914-918)
+        for (int k = 0; k < 3; ++k) {
+            float v = (float)gq[(17 + k) * P];
+            o[c++] = w != 0 ? v / w : v;
+        }
     if (channels & B200PT_GBUFFER_POSITION)
         for (int k = 0; k < 3; ++k) {
             float v = (float)gq[(1 + k) * P];

@@ -415,6 +415,7 @@ int b200pt_film_gbuffer_image(b200pt_render *r, uint32_t channels, float *out, i
     }
     int nc = 3;
     if (channels & B200PT_GBUFFER_RADIANCE) nc += r->dev.film.nBuckets;
+    if (channels & B200PT_GBUFFER_ALBEDO) nc += 3;
     if (channels & B200PT_GBUFFER_POSITION) nc += 3;
     if (channels & B200PT_GBUFFER_MATERIAL) nc += 1;
     if (channels & B200PT_GBUFFER_INSTANCE) nc += 1;
@@ -447,6 +448,7 @@ int b200pt_film_write_exr(b200pt_render *r, uint32_t channels, const char *path,
     };
     if (film.type == 2) {
         if (channels & B200PT_GBUFFER_RADIANCE) numbered("Radiance.C", nB);
+        if (channels & B200PT_GBUFFER_ALBEDO) for (const char *c : {"Albedo.R", "Albedo.G", "Albedo.B"}) names.push_back(c);
         if (channels & B200PT_GBUFFER_POSITION) for (const char *c : {"P.X", "P.Y", "P.Z"}) names.push_back(c);
         if (channels & B200PT_GBUFFER_MATERIAL) names.push_back("MaterialId");
         if (channels & B200PT_GBUFFER_INSTANCE) names.push_back("InstanceId");

@@ -163,6 +163,19 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
     rs.film.maxComponentValue = d->max_component_value;
     std::memcpy(rs.film.outputRGBFromSensorRGB, d->output_rgb_from_sensor_rgb, 36);
     for (int c = 0; c < 3; ++c) rs.film.sensorSpectrum[c] = d->sensor_spectrum[c];
+    rs.film.gbufferAlbedo = (d->film_type == 2 && d->gbuffer_albedo) ? 1u : 0u;
+    rs.film.albedoIlluminant = 0;
+    for (int c = 0; c < 3; ++c) rs.film.xyzSpectrum[c] = 0;
+    std::memset(rs.film.rgbFromXYZ, 0, sizeof(rs.film.rgbFromXYZ));
+    if (rs.film.gbufferAlbedo) {
+        for (int c = 0; c < 3; ++c) {
+            if (!specOk(d->gbuffer_xyz_spectrum[c])) return bad("gbuffer_albedo: gbuffer_xyz_spectrum index out of range");
+            rs.film.xyzSpectrum[c] = d->gbuffer_xyz_spectrum[c];
+        }
+        if (!specOk(d->gbuffer_illuminant)) return bad("gbuffer_albedo: gbuffer_illuminant index out of range");
+        rs.film.albedoIlluminant = d->gbuffer_illuminant;
+        std::memcpy(rs.film.rgbFromXYZ, d->gbuffer_rgb_from_xyz, 36);
+    }
     // ZSobolSampler constructor (samplers.h:228-238)
     rs.sampler.type = d->sampler_type;  // 1: IndependentSampler, which only uses samplesPerPixel and seed
     rs.sampler.samplesPerPixel = d->samples_per_pixel;
@@ -306,6 +319,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         if (((m.type == MAT_DIFFUSE || m.type == MAT_DIELECTRIC) && m.params[4] != 0) || (m.type == MAT_COATED_DIFFUSE && m.params[8] != 0))
             out.rs.geomExt = 1u;
     if (d->sampler_type != B200PT_SAMPLER_ZSOBOL) out.rs.geomExt = 1u;
+    if (out.rs.film.gbufferAlbedo) out.rs.geomExt = 1u;  // the albedo estimate lives in the EXT = 1 shading kernels
     for (uint32_t i = 0; i < d->n_lights; ++i)
         if (d->lights[i].type >= B200PT_LIGHT_POINT) out.rs.geomExt = 1u;
     out.lights.resize(d->n_lights);

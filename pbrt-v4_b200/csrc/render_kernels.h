@@ -17,10 +17,10 @@ constexpr uint32_t kConsumedTag = 0xFFFFFFFDu;  // hit slot of a ray the medium 
 constexpr int kVolMaxIterations = 96;  // wavefront iterations of a volpath pass (interfaces do not count as depth)
 constexpr int kMatQueues = 4;     // one shading queue per MaterialType
 constexpr int kCountStride = 8;   // ints per depth in PassBuffers::counts
-constexpr int kAovWords = 12;     // PassBuffers::aov planes
+constexpr int kAovWords = 18;     // PassBuffers::aov planes: {set, p, n, ns, material, instance}, then the albedo's XYZ twice (below)
 // GBufferFilm accumulators behind the rgbw and the 2 x 31 bucket planes, one plane of nPixels doubles each:
 // gBufferWeightSum, pSum[3], nSum[3], nsSum[3], sum rgb[3], sum rgb^2[3], n (VarianceEstimator as sums)
-constexpr int kGBufferPlanes = 17;
+constexpr int kGBufferPlanes = 20;  // ..., 17-19: rgbAlbedoSum
 
 // One pass = nPixels x nSamplesInPass paths; path i is pixel i % nPixels, sample slot i / nPixels.
 // Path state is indexed by path id and laid out [field][path] so a warp's accesses coalesce; the

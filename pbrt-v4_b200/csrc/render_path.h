@@ -487,6 +487,42 @@ B2_SPECTRAL_LOOP
     // BSDF shading frame: Frame::FromXZ(Normalize(dpdus), ns) (bsdf.h:24-25)
     V3 fx = Normalize(si.dpdus), fz = si.ns, fy = Cross(fz, fx);
     V3 woL = mk(Dot(wo, fx), Dot(wo, fy), Dot(wo, fz));
+    // GBufferFilm's albedo of the first visible surface (cpu/integrators.cpp:690-711): bsdf.rho(isect.wo, ucRho, uRho),
+    // 16 BSDF samples at fixed points; kept as the XYZ of albedo * illuminant (SampledSpectrum::ToXYZ, util/spectrum.cpp)
+    // under both wavelength pdfs the path can end with (the film converts with the final lambda, film.cpp:640-642)
+    if (EXT && p.depth == 0 && rs.film.gbufferAlbedo && io.WantsAlbedo()) {
+        const float ucRho[16] = {0.75741637f, 0.37870818f, 0.7083487f, 0.18935409f, 0.9149363f, 0.35417435f, 0.5990858f, 0.09467703f,
+                                 0.8578725f, 0.45746812f, 0.686759f, 0.17708716f, 0.9674518f, 0.2995429f, 0.5083201f, 0.047338516f};
+        const float uRho[16][2] = {{0.855985f, 0.570367f}, {0.381823f, 0.851844f}, {0.285328f, 0.764262f}, {0.733380f, 0.114073f},
+                                   {0.542663f, 0.344465f}, {0.127274f, 0.414848f}, {0.964700f, 0.947162f}, {0.594089f, 0.643463f},
+                                   {0.095109f, 0.170369f}, {0.825444f, 0.263359f}, {0.429467f, 0.454469f}, {0.244460f, 0.816459f},
+                                   {0.756135f, 0.731258f}, {0.516165f, 0.152852f}, {0.180888f, 0.214174f}, {0.898579f, 0.503897f}};
+        float alb[kNLambda];
+        for (int k = 0; k < kNLambda; ++k) alb[k] = 0;
+        const V3 woRho = mk(Dot(si.wo, fx), Dot(si.wo, fy), Dot(si.wo, fz));  // RenderToLocal(isect.wo)
+        for (int i = 0; i < 16 && woRho.z != 0; ++i) {  // BxDF::rho (bxdfs.cpp:1135-1148)
+            BsdfEval ev;
+            BsdfSample bs = EvalSample(rs, p.lambdaU, bsdf, woRho, ucRho[i], uRho[i][0], uRho[i][1], ev, spec8);
+            if (!bs.ok || !(bs.pdf > 0)) continue;
+            const float c = AbsCosTheta(bs.wi) / bs.pdf;
+            LambdaIter li(p.lambdaU);
+            for (int k = 0; k < kNLambda; ++k, li.Next())
+                alb[k] += BsdfSpectral<EXT>(rs, bsdf, ev, li.lam, cachesR ? io.R(k) : 0.f, k, spec8) * c;
+        }
+        float xyz[6] = {0, 0, 0, 0, 0, 0};
+        const float pdfU = 1 / (kLambdaMax - kLambdaMin);
+        LambdaIter li(p.lambdaU);
+        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+            const float a = (alb[k] / 16) * SpectrumAt(rs.spectra[rs.film.albedoIlluminant], li.lam);
+            for (int c = 0; c < 3; ++c) {
+                const float v = SpectrumAt(rs.spectra[rs.film.xyzSpectrum[c]], li.lam) * a;
+                xyz[c] += v / pdfU;
+                if (k == 0) xyz[3 + c] = v / (pdfU / kNLambda);  // after TerminateSecondary: pdf[0] / N, the rest 0
+            }
+        }
+        for (int c = 0; c < 6; ++c) xyz[c] = xyz[c] / kNLambda / kCIE_Y_integral;
+        io.VisibleSurfaceAlbedo(xyz);
+    }
 
     if (p.depth++ == rs.integrator.maxDepth) {
         KillPath(p);
@@ -736,7 +772,6 @@ B2_SPECTRAL_LOOP
 // integrator returned it (after the NaN / Inf guard of cpu/integrators.cpp:270-279), NOT divided by the
 // wavelength pdf; after TerminateSecondary the secondary wavelengths are added too, as the reference does.
 // acc(bucket, value, weight) performs `bucketSums[b] += value; weightSums[b] += weight` in doubles.
-constexpr float kCIE_Y_integral = 106.856895f;  // util/spectrum.h:31
 B2_HD int LambdaToBucket(float lambda, int nBuckets) {  // film.h:534-539
     int bucket = (int)(nBuckets * (lambda - kLambdaMin) / (kLambdaMax - kLambdaMin));
     return bucket < 0 ? 0 : (bucket > nBuckets - 1 ? nBuckets - 1 : bucket);

@@ -6,6 +6,7 @@
 
 namespace b200pt {
 
+constexpr float kCIE_Y_integral = 106.856895f;  // util/spectrum.h:31
 constexpr int kNLambda = 31;          // NSpectrumSamples of the ISET fork (util/spectrum.h:36)
 constexpr float kLambdaMin = 395.f;   // Lambda_min / Lambda_max (util/spectrum.h:34-35)
 constexpr float kLambdaMax = 705.f;
@@ -115,6 +116,11 @@ struct FilmDev {
     int32_t sensorSpectrum[3];   // r_bar, g_bar, b_bar tables
     // GBufferFilm: render space -> the AOVs' output space (points through outM; normals through the transpose of outMInv)
     float outM[16], outMInv[16];
+    // GBufferFilm's Albedo.* (film.cpp:640-644): computed when gbufferAlbedo != 0.  albedo * illuminant -> XYZ through the
+    // CIE matching functions (spectra tables) -> rgbFromXYZ (the film colour space's)
+    uint32_t gbufferAlbedo;
+    int32_t xyzSpectrum[3], albedoIlluminant;
+    float rgbFromXYZ[9];
 };
 
 struct SamplerDev {

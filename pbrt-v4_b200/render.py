@@ -101,6 +101,11 @@ class RenderScene:
             ids = np.ascontiguousarray(d["material_ids"], np.int32)
             keep.append(ids)
             r.material_ids = ids.ctypes.data_as(C.POINTER(C.c_int32))
+            if "gbuffer_albedo" in d:  # saveAlbedo: {X, Y, Z, illuminant} spectrum indices, RGBFromXYZ
+                r.gbuffer_albedo = 1
+                r.gbuffer_xyz_spectrum[:] = [int(x) for x in d["gbuffer_albedo"][:3]]
+                r.gbuffer_illuminant = int(d["gbuffer_albedo"][3])
+                r.gbuffer_rgb_from_xyz[:] = [float(x) for x in d["gbuffer_rgb_from_xyz"].reshape(-1)]
         if r.film_type in (1, 2):  # SpectralFilm / GBufferFilm buckets
             r.n_buckets = int(d["film_spectral"][0])
             r.lambda_min, r.lambda_max = float(d["film_spectral"][1]), float(d["film_spectral"][2])

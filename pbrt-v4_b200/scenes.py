@@ -386,11 +386,11 @@ LIGHTS = {
 GBUFFER_ALL = 1 | 2 | 4 | 8 | 16 | 32 | 64 | 128
 
 
-def _gbuffer_film(out, xres, yres):
+def _gbuffer_film(out, xres, yres, albedo=False):
     return (f'Film "gbuffer" "string filename" "{os.path.splitext(out)[0]}.exr" "integer xresolution" {xres} '
             f'"integer yresolution" {yres} "bool savefp16" false "bool saveRadiance" true "bool saveDepth" true '
             '"bool saveMaterial" true "bool saveInstance" true "bool saveNormal" true "bool saveNs" true '
-            '"bool saveVariance" true "bool saveRelativeVariance" true')
+            '"bool saveVariance" true "bool saveRelativeVariance" true' + (' "bool saveAlbedo" true' if albedo else ''))
 
 
 def _envmap_lines(path, res):
@@ -428,7 +428,7 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
         'PixelFilter ' + (pixelfilter if pixelfilter.startswith('"') else f'"{pixelfilter}"'),  # a name, or name + parameters
         (f'Film "rgb" "string filename" "{out}" "integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false'
          if film == "rgb" else
-         _gbuffer_film(out, res, res) if film == "gbuffer" else
+         _gbuffer_film(out, res, res, albedo=film == "gbuffer_albedo") if film in ("gbuffer", "gbuffer_albedo") else
          # SpectralFilm (film.h:430-560) only accepts an .exr name; the oracle reads its Image out directly
          f'Film "spectral" "string filename" "{os.path.splitext(out)[0]}.exr" "integer nbuckets" {nbuckets} '
          f'"integer xresolution" {res} "integer yresolution" {res} "bool savefp16" false'),

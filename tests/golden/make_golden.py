@@ -71,6 +71,10 @@ RENDER_CASES = {
     # GBufferFilm (the ISET film): RGB + 31 radiance channels + position / ids / normals / variance AOVs, on the
     # instanced Cornell box with smooth-shaded meshes (shading normals differ from the geometric ones, instance ids)
     "cornell_gbuffer_r48_s16": dict(res=48, spp=16, maxdepth=5, film="gbuffer", smooth="instanced"),
+    # ... with saveAlbedo: Albedo.R G B from bsdf.rho at the first visible surface (diffuse walls, a rough copper box, a
+    # dielectric one whose dispersive index terminates the secondary wavelengths: the film converts with the final lambda)
+    "cornell_gbuffer_albedo_r48_s16": dict(res=48, spp=16, maxdepth=5, film="gbuffer_albedo",
+                                           boxes=("conductor_rough", "dielectric_glass")),
     "cornell_coated_r64_s16": dict(res=64, spp=16, maxdepth=5, boxes=("coated_diffuse", "coated_diffuse_rough")),
     "cornell_glass_r64_s16": dict(res=64, spp=16, maxdepth=6, boxes=("dielectric_smooth", "dielectric_glass")),
     # bilinear patch meshes shaded (BilinearPatch::InteractionFromIntersection), one under ReverseOrientation
@@ -272,7 +276,7 @@ def make_render_goldens(P, refrun, out):
         with tempfile.TemporaryDirectory() as tmp:
             pbrt, pfm = os.path.join(tmp, name + ".pbrt"), os.path.join(tmp, name + ".pfm")
             P.scenes.cornell_pbrt(pbrt, out=pfm, **kw)
-            if kw.get("film") in ("spectral", "gbuffer"):  # no EXR writer in the oracle build: Film::GetImage read directly
+            if kw.get("film") in ("spectral", "gbuffer", "gbuffer_albedo"):  # no EXR writer in the oracle build: Film::GetImage read directly
                 img, _, secs = refrun.render_channels(pbrt)
             else:
                 img, secs = refrun.render(pbrt, pfm)

@@ -52,6 +52,8 @@ struct HostIO {
     float R(int k) const { return refl[k]; }
     void SetR(int k, float v) { refl[k] = v; }
     void VisibleSurface(V3, V3, V3, int, int) {}
+    bool WantsAlbedo() const { return false; }
+    void VisibleSurfaceAlbedo(const float *) {}
     void AddL(int k, float v) { L[k] += v; }
     void ShadowBegin() {}
     void SetLd(int k, float v) { Ld[k] = v; }

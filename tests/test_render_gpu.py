@@ -390,6 +390,31 @@ def test_gbuffer_film_matches_reference(P):
     np.testing.assert_allclose(striped[..., 39:], img[..., 39:], rtol=2e-4, atol=1e-5)
 
 
+def test_gbuffer_albedo_matches_reference(P):
+    """GBufferFilm's Albedo.R G B (film.cpp:640-644, 846-858): bsdf.rho over the reference's 16 fixed sample points at the
+    first visible surface (cpu/integrators.cpp:690-711), times the colour space's illuminant, to RGB with the wavelength pdf
+    the path ENDS with.  Diffuse walls, rough copper, dispersive glass (smooth: rho of a specular BSDF)."""
+    name = "cornell_gbuffer_albedo_r48_s16"
+    rsc = P.RenderScene.load(os.path.join(GOLD, name + ".b2rs"))
+    ref = np.load(os.path.join(GOLD, name + "_ref.npy"))
+    assert ref.shape[-1] == 3 + 31 + 3 + 3 + 1 + 1 + 3 + 3 + 3 + 3
+    r = P.B200Renderer(rsc)
+    try:
+        r.render()
+        img = r.gbuffer_image(P.scenes.GBUFFER_ALL | P.capi.GBUFFER_ALBEDO)
+    finally:
+        r.close()
+    assert img.shape == ref.shape
+    alb, ralb = img[..., 34:37].astype(np.float64), ref[..., 34:37].astype(np.float64)
+    assert ralb.mean() > 0.2 and ralb.std() > 0.05  # the reference's albedo channel is not flat
+    err = np.sqrt(np.mean((alb - ralb) ** 2)) / np.mean(np.abs(ralb))
+    assert err <= 2e-3, err
+    # the other groups sit three channels further on and still agree (the glass box makes the image noise-gated: not here)
+    for sl in (slice(37, 40), slice(42, 45), slice(45, 48)):  # P, Ns, N
+        a, b = img[..., sl].astype(np.float64), ref[..., sl].astype(np.float64)
+        assert np.sqrt(np.mean((a - b) ** 2)) / max(np.mean(np.abs(b)), 1e-12) <= 1e-3
+
+
 def test_config4_gbuffer_matches_reference(P):
     """BASELINE configs[3] in miniature on the film it is quoted on: RealisticCamera + GBufferFilm (R G B + Radiance.C01-31
     + AOVs), path for path against the reference's Film::GetImage."""
