@@ -64,13 +64,14 @@ def test_wavefront_over_b200_aggregate(P, dropin, tmp_path, kind):
     assert rrmse(img, ref) <= 1e-5, rrmse(img, ref)
 
 
-def test_render_b200_gbuffer_exr(P, dropin, tmp_path):
+@pytest.mark.parametrize("film", ["gbuffer", "gbuffer_albedo"])
+def test_render_b200_gbuffer_exr(P, dropin, tmp_path, film):
     """A .pbrt with the ISET film (`Film "gbuffer"`, EXR only) through the compiled drop-in: the reference's parser and
     scene objects, the GPU frame, the file written by b200pt_film_write_exr (device-side packing) - against the
     reference's own Film::GetImage of the same file (dumpscene_ref --render; the oracle build has no EXR writer)."""
     from conftest import read_exr
     pbrt, out = str(tmp_path / "g.pbrt"), str(tmp_path / "g.exr")
-    P.scenes.cornell_pbrt(pbrt, out=out, res=48, spp=16, maxdepth=5, film="gbuffer", smooth="instanced")
+    P.scenes.cornell_pbrt(pbrt, out=out, res=48, spp=16, maxdepth=5, film=film, smooth="instanced")  # (_albedo: saveAlbedo)
     ref, names, _ = dropin.render_channels(pbrt)
     _, _, log = dropin.render_b200(pbrt, None)
     assert "samples in" in log
