@@ -493,6 +493,26 @@ int b200pt_render_get_stats(const b200pt_render *r, b200pt_render_stats *out);
 int b200pt_bvh2_build(const float *bounds, uint32_t n, int max_prims_in_node,
                       void *nodes_out, uint32_t *n_nodes_out, uint32_t *order_out);
 
+/* Host-only: a PLY mesh file as the reference's `Shape "plymesh"` reads it (TriQuadMesh::ReadPLY,
+ * util/mesh.cpp:322-423): vertex x y z, optional nx ny nz, optional (u, v) named u v / s t / texture_u texture_v /
+ * texture_s texture_t, faces of three or four vertices from the list property `vertex_indices` (other lengths are
+ * passed over), optional face_indices; ascii, binary_little_endian, binary_big_endian (gzip refused).  A quad comes
+ * out in bilinear-patch order p00 p10 p01 p11 (mesh.cpp:299-305), ready for a B200PT_MESH_BILINEAR mesh;
+ * whether quads are split into triangles instead (TriQuadMesh::ConvertToOnlyTriangles, mesh.cpp:425-442) is the host's choice.
+ * The arrays are malloc'ed; b200pt_ply_free releases them.  On failure: B200PT_ERR_INVALID and, if err != NULL, the
+ * reason in err (the reference's message where it has one).  Needs no GPU. */
+typedef struct b200pt_ply_mesh {
+    uint64_t n_vertices, n_triangles, n_quads, n_face_indices;
+    float *p;              /* 3 per vertex */
+    float *n;              /* 3 per vertex, or NULL */
+    float *uv;             /* 2 per vertex, or NULL */
+    int32_t *tri_indices;  /* 3 per triangle, or NULL */
+    int32_t *quad_indices; /* 4 per quad, or NULL */
+    int32_t *face_indices; /* n_face_indices entries, or NULL */
+} b200pt_ply_mesh;
+int b200pt_ply_read(const char *path, b200pt_ply_mesh *out, char *err, uint64_t err_len);
+void b200pt_ply_free(b200pt_ply_mesh *m);
+
 #ifdef __cplusplus
 }
 #endif

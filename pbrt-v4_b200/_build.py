@@ -18,7 +18,7 @@ NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nv
 CUDA_HOME = os.path.dirname(os.path.dirname(NVCC))
 GENCODE = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
-CPP_SOURCES = ["bvh2_build.cpp", "wide_build.cpp", "scene_host.cpp", "render_host.cpp", "api.cpp", "render_api.cpp"]
+CPP_SOURCES = ["bvh2_build.cpp", "wide_build.cpp", "scene_host.cpp", "render_host.cpp", "api.cpp", "render_api.cpp", "ply_read.cpp"]
 # (file, extra nvcc flags)
 CU_SOURCES = [
     ("traverse_bvh2.cu", ["--fmad=false"]),

@@ -84,7 +84,39 @@ SYMBOLS = {
     "b200pt_get_trace_stats": (C.c_int, [C.c_void_p, C.POINTER(TraceStats)]),
     "b200pt_bvh2_build": (C.c_int, [C.POINTER(C.c_float), C.c_uint32, C.c_int, C.c_void_p,
                                     C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "b200pt_ply_read": (C.c_int, [C.c_char_p, C.c_void_p, C.c_char_p, C.c_uint64]),
+    "b200pt_ply_free": (None, [C.c_void_p]),
 }
+
+
+class PlyMesh(C.Structure):  # b200pt_ply_mesh
+    _fields_ = [("n_vertices", C.c_uint64), ("n_triangles", C.c_uint64), ("n_quads", C.c_uint64), ("n_face_indices", C.c_uint64),
+                ("p", C.POINTER(C.c_float)), ("n", C.POINTER(C.c_float)), ("uv", C.POINTER(C.c_float)),
+                ("tri_indices", C.POINTER(C.c_int32)), ("quad_indices", C.POINTER(C.c_int32)),
+                ("face_indices", C.POINTER(C.c_int32))]
+
+
+def read_ply(path):
+    """b200pt_ply_read -> dict of numpy arrays {p [nv,3], n | None, uv | None, tri [nt,3], quad [nq,4], face_indices | None}
+    (copies; the library's arrays are freed before returning).  Raises B200PTError with the library's message."""
+    import numpy as np
+    m, err = PlyMesh(), C.create_string_buffer(512)
+    rc = lib().b200pt_ply_read(str(path).encode(), C.byref(m), err, 512)
+    if rc != 0:
+        raise B200PTError(rc, err.value.decode())
+    try:
+        def arr(ptr, n, cols, dt):
+            if not ptr or n == 0:
+                return None
+            return np.ctypeslib.as_array(ptr, shape=(int(n) * cols,)).astype(dt).reshape(int(n), cols).copy()
+        out = {"p": arr(m.p, m.n_vertices, 3, np.float32), "n": arr(m.n, m.n_vertices, 3, np.float32),
+               "uv": arr(m.uv, m.n_vertices, 2, np.float32), "tri": arr(m.tri_indices, m.n_triangles, 3, np.int32),
+               "quad": arr(m.quad_indices, m.n_quads, 4, np.int32)}
+        fi = arr(m.face_indices, m.n_face_indices, 1, np.int32)
+        out["face_indices"] = None if fi is None else fi.reshape(-1)
+        return out
+    finally:
+        lib().b200pt_ply_free(C.byref(m))
 
 _lib = None
 
