@@ -284,6 +284,15 @@ typedef struct b200pt_medium {
     const float *density;
     int32_t mres[3];
     const float *majorants;
+    /* emission (HomogeneousMedium / GridMedium::SamplePoint, media.h:217-262, 288-318): emissive != 0 adds, at every
+     * tentative collision, sigma_a * Le (cpu/integrators.cpp:990-1001).  le_spectrum = Le_spec (a homogeneous medium's
+     * already times its Lescale / photometric normalisation, as the object holds it).  Grid media: le_scale = the LeScale
+     * grid, le_nx x le_ny x le_nz values (1 x 1 x 1 when the scene gave no "Lescale" array; trilinear with zeros outside,
+     * like the density).  Temperature grids (blackbody emission) are not taken. */
+    uint32_t emissive;
+    int32_t le_spectrum;
+    int32_t le_nx, le_ny, le_nz;
+    const float *le_scale;
 } b200pt_medium;
 
 typedef struct b200pt_render_desc {

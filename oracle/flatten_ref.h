@@ -564,16 +564,18 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         w.i32("camera_medium", {1}, {mediumIndex(camMedium)});
         // media_i: {type, sigma_a, sigma_s, nx, ny, nz, mres[3]}; media_f: {g, bounds[6], mediumFromRender[16],
         // renderFromMedium[16]} (include/b200pt.h b200pt_medium)
-        std::vector<int32_t> mi;
+        std::vector<int32_t> mi, mle;
         std::vector<float> mf;
         int k = 0;
         for (auto &kv : media) {
             Medium m = kv.second;
-            if (m.IsEmissive()) die("emissive media are not dumped");
+            // media_le: {Le_spec or -1, LeScale grid nx ny nz} per medium; medium_lescale_<k>: the grid of an emissive grid medium
+            int32_t le[4] = {-1, 0, 0, 0};
             float rec[39] = {0};
             if (const HomogeneousMedium *hm = m.CastOrNullptr<HomogeneousMedium>()) {
                 mi.insert(mi.end(), {0, pool.add(&hm->sigma_a_spec, 0), pool.add(&hm->sigma_s_spec, 0), 0, 0, 0, 0, 0, 0});
                 rec[0] = hm->phase.g;
+                if (m.IsEmissive()) le[0] = pool.add(&hm->Le_spec, 0);  // (already times Lescale / its photometric norm)
             } else if (const GridMedium *gm = m.CastOrNullptr<GridMedium>()) {
                 const SampledGrid<Float> &dg = gm->densityGrid;
                 const MajorantGrid &mg = gm->majorantGrid;
@@ -589,13 +591,25 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
                 std::vector<float> dens(dg.values.begin(), dg.values.end()), maj(mg.voxels.begin(), mg.voxels.end());
                 w.f32("medium_density_" + std::to_string(k), {uint32_t(dg.nz), uint32_t(dg.ny), uint32_t(dg.nx)}, dens);
                 w.f32("medium_majorants_" + std::to_string(k), {uint32_t(mg.res.z), uint32_t(mg.res.y), uint32_t(mg.res.x)}, maj);
+                if (m.IsEmissive()) {
+                    if (gm->temperatureGrid) die("grid media with a temperature grid (blackbody emission) are not dumped");
+                    const SampledGrid<Float> &lg = gm->LeScale;
+                    le[0] = pool.add(&gm->Le_spec, 0);
+                    le[1] = lg.nx;
+                    le[2] = lg.ny;
+                    le[3] = lg.nz;
+                    std::vector<float> lv(lg.values.begin(), lg.values.end());
+                    w.f32("medium_lescale_" + std::to_string(k), {uint32_t(lg.nz), uint32_t(lg.ny), uint32_t(lg.nx)}, lv);
+                }
             } else
                 die("only homogeneous and uniformgrid media are dumped so far");
             mf.insert(mf.end(), rec, rec + 39);
+            mle.insert(mle.end(), le, le + 4);
             ++k;
         }
         w.i32("media_i", {uint32_t(k), 9}, mi);
         w.f32("media_f", {uint32_t(k), 39}, mf);
+        w.i32("media_le", {uint32_t(k), 4}, mle);
     }
     if (!instObject.empty()) {
         w.i32("instance_object", {uint32_t(instObject.size())}, instObject);

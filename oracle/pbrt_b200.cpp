@@ -316,6 +316,17 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
                 M.density = T.at("medium_density_" + std::to_string(k)).f();
                 M.majorants = T.at("medium_majorants_" + std::to_string(k)).f();
             }
+            if (T.has("media_le") && T.at("media_le").i()[4 * k] >= 0) {
+                const int32_t *le = T.at("media_le").i() + 4 * k;
+                M.emissive = 1;
+                M.le_spectrum = le[0];
+                if (M.type == 1) {
+                    M.le_nx = le[1];
+                    M.le_ny = le[2];
+                    M.le_nz = le[3];
+                    M.le_scale = T.at("medium_lescale_" + std::to_string(k)).f();
+                }
+            }
         }
         r.n_media = uint32_t(mdi.rows());
         r.media = m.media.data();

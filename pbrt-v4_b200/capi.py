@@ -190,7 +190,9 @@ class Medium(C.Structure):
     _fields_ = [("type", C.c_uint32), ("sigma_a", C.c_int32), ("sigma_s", C.c_int32), ("g", C.c_float),
                 ("bounds", C.c_float * 6), ("medium_from_render", C.c_float * 16),
                 ("render_from_medium", C.c_float * 16), ("nx", C.c_int32), ("ny", C.c_int32), ("nz", C.c_int32),
-                ("density", C.POINTER(C.c_float)), ("mres", C.c_int32 * 3), ("majorants", C.POINTER(C.c_float))]
+                ("density", C.POINTER(C.c_float)), ("mres", C.c_int32 * 3), ("majorants", C.POINTER(C.c_float)),
+                ("emissive", C.c_uint32), ("le_spectrum", C.c_int32), ("le_nx", C.c_int32), ("le_ny", C.c_int32),
+                ("le_nz", C.c_int32), ("le_scale", C.POINTER(C.c_float))]
 
 
 class RenderDesc(C.Structure):

@@ -133,6 +133,12 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
         r->dGrids.push_back(dm);
         r->host.media[i].density = (const float *)dd;
         r->host.media[i].majorants = (const float *)dm;
+        if (!r->host.mediumLeGrids[i].empty()) {
+            void *dl = nullptr;
+            if ((rc = Upload(ctx, r->host.mediumLeGrids[i], &dl))) return fail(rc);
+            r->dGrids.push_back(dl);
+            r->host.media[i].leScale = (const float *)dl;
+        }
     }
     if ((rc = Upload(ctx, r->host.media, &r->dMedia))) return fail(rc);
     r->nPixels = r->host.width * r->host.height;

@@ -199,6 +199,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         rs.nMedia = d->n_media;
         out.media.resize(d->n_media);
         out.mediumGrids.resize(d->n_media);
+        out.mediumLeGrids.resize(d->n_media);
         for (uint32_t i = 0; i < d->n_media; ++i) {
             const b200pt_medium &m = d->media[i];
             if (m.type > B200PT_MEDIUM_GRID) return bad("unsupported medium type");
@@ -220,6 +221,16 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                 for (int c = 0; c < 3; ++c) o.mres[c] = m.mres[c];
                 out.mediumGrids[i].first.assign(m.density, m.density + size_t(m.nx) * m.ny * m.nz);
                 out.mediumGrids[i].second.assign(m.majorants, m.majorants + size_t(m.mres[0]) * m.mres[1] * m.mres[2]);
+            }
+            if (m.emissive) {
+                if (!specOk(m.le_spectrum)) return bad("emissive medium: le_spectrum index out of range");
+                o.emissive = 1;
+                o.le = m.le_spectrum;
+                if (m.type == B200PT_MEDIUM_GRID) {
+                    if (m.le_nx < 1 || m.le_ny < 1 || m.le_nz < 1 || !m.le_scale) return bad("emissive grid medium without an LeScale grid");
+                    o.lnx = m.le_nx; o.lny = m.le_ny; o.lnz = m.le_nz;
+                    out.mediumLeGrids[i].assign(m.le_scale, m.le_scale + size_t(m.le_nx) * m.le_ny * m.le_nz);
+                }
             }
         }
     }

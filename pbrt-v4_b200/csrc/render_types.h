@@ -77,6 +77,12 @@ struct MediumDev {
     int32_t mres[3];
     const float *density;
     const float *majorants;
+    // emission (media.h:217-262, 288-318): Le_spec (spectrum table; a homogeneous medium's is already scaled) times, for a
+    // grid medium, the LeScale grid at the point (its own resolution: 1 x 1 x 1 when the scene gave one number)
+    uint32_t emissive;
+    int32_t le;
+    int32_t lnx, lny, lnz;
+    const float *leScale;  // null: homogeneous
 };
 
 struct CameraDev {

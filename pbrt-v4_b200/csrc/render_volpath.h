@@ -138,7 +138,7 @@ B2_HD void VolMediumBegin(const RenderSceneDev &rs, PathRegs &p, float tHit, Vol
 // one step of the walk; TMAJ_GO_ON = call again
 template <class IO>
 B2_HD int VolMediumWalkStep(const RenderSceneDev &rs, PathRegs &p, VolMediumState &st, IO &io) {
-    PathMediumCB<IO> cb(io, st.rng, st.sigA, st.sigS, st.sigT, p.depth, rs.integrator.maxDepth);
+    PathMediumCB<IO> cb(io, st.rng, st.sigA, st.sigS, st.sigT, p.depth, rs.integrator.maxDepth, rs, rs.media[p.medium], p.lambdaU);
     int r = st.walk.Step(rs.media[p.medium], st.sigT, st.rng, st.T_maj, cb);
     st.terminated |= cb.terminated;
     if (cb.scattered) {
@@ -168,7 +168,7 @@ B2_HD void VolMediumBeginFast(const RenderSceneDev &rs, PathRegs &p, float tHit,
 // the pending collision; false = the walk is over (st.T_maj all ones, as the reference leaves it)
 template <class IO>
 B2_HD bool VolMediumCollide(const RenderSceneDev &rs, PathRegs &p, VolMediumState &st, TMajFastWalk &fw, IO &io) {
-    PathMediumCB<IO> cb(io, st.rng, st.sigA, st.sigS, st.sigT, p.depth, rs.integrator.maxDepth);
+    PathMediumCB<IO> cb(io, st.rng, st.sigA, st.sigS, st.sigT, p.depth, rs.integrator.maxDepth, rs, rs.media[p.medium], p.lambdaU);
     const bool goOn = fw.Collide(rs.media[p.medium], st.sigT, st.T_maj, cb);
     st.terminated |= cb.terminated;
     if (cb.scattered) {

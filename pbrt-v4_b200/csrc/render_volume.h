@@ -78,6 +78,23 @@ B2_HD V3 BoundsOffset(const float *b, V3 p) {
     if (b[5] > b[2]) o.z /= b[5] - b[2];
     return o;
 }
+// GridMedium's LeScale.Lookup(p) at a render-space point (media.h:303-305): the same trilinear lookup, zero outside
+B2_HD float MediumLeScaleAt(const MediumDev &m, V3 p) {
+    V3 q = BoundsOffset(m.bounds, XformPoint(m.mediumFromRender, p));
+    auto at = [&](int x, int y, int z) -> float {
+        if (x < 0 || y < 0 || z < 0 || x >= m.lnx || y >= m.lny || z >= m.lnz) return 0.f;
+        return m.leScale[((long long)z * m.lny + y) * m.lnx + x];
+    };
+    float sx = q.x * m.lnx - .5f, sy = q.y * m.lny - .5f, sz = q.z * m.lnz - .5f;
+    float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    float dx = sx - fx, dy = sy - fy, dz = sz - fz;
+    float d00 = Lerp(dx, at(ix, iy, iz), at(ix + 1, iy, iz));
+    float d10 = Lerp(dx, at(ix, iy + 1, iz), at(ix + 1, iy + 1, iz));
+    float d01 = Lerp(dx, at(ix, iy, iz + 1), at(ix + 1, iy, iz + 1));
+    float d11 = Lerp(dx, at(ix, iy + 1, iz + 1), at(ix + 1, iy + 1, iz + 1));
+    return Lerp(dz, Lerp(dy, d00, d10), Lerp(dy, d01, d11));
+}
 // density scaling sigma_a / sigma_s at a render-space point (GridMedium::SamplePoint, media.h:288-300)
 B2_HD float MediumDensityAt(const MediumDev &m, V3 p) {
     if (m.type == 0) return 1.f;
@@ -358,8 +375,7 @@ B2_SPECTRAL_LOOP
     }
 }
 
-// Delta tracking along the path ray: the callback of VolPathIntegrator::Li (cpu/integrators.cpp:976-1063), media
-// without emission.  Real scattering only updates beta / r_u and records the point; the caller samples the light
+// Delta tracking along the path ray: the callback of VolPathIntegrator::Li (cpu/integrators.cpp:976-1063).  Real scattering only updates beta / r_u and records the point; the caller samples the light
 // and the phase function right after the walk ends (nothing else happens in between in the reference).
 template <class IO>
 struct PathMediumCB {
@@ -370,8 +386,38 @@ struct PathMediumCB {
     int maxDepth;
     bool terminated = false, scattered = false;
     V3 pScatter;
-    B2_HD PathMediumCB(IO &i, PCG32 &r, const float *a, const float *s, const float *t, int &d, int md)
-        : io(i), rng(r), sigA(a), sigS(s), sigT(t), depth(d), maxDepth(md) { pScatter = mk(0, 0, 0); }
+    const RenderSceneDev &rs;  // an emissive medium's Le_spec at the path's wavelengths
+    const MediumDev &m;
+    float lambdaU;
+    B2_HD PathMediumCB(IO &i, PCG32 &r, const float *a, const float *s, const float *t, int &d, int md, const RenderSceneDev &scene,
+                       const MediumDev &medium, float lu)
+        : io(i), rng(r), sigA(a), sigS(s), sigT(t), depth(d), maxDepth(md), rs(scene), m(medium), lambdaU(lu) { pScatter = mk(0, 0, 0); }
+    // "Add emission from medium scattering event" (cpu/integrators.cpp:990-1001): at EVERY tentative collision
+    B2_HD void AddEmission(V3 p, float density, float majScale, const float *T_maj) {
+        float scale = 1.f;
+        if (m.leScale) {  // GridMedium::SamplePoint (media.h:301-318): nothing where LeScale <= 0
+            scale = MediumLeScaleAt(m, p);
+            if (!(scale > 0)) return;
+        }
+        const float pdf = (sigT[0] * majScale) * T_maj[0];
+        float sumRe = 0;
+        bool anyRe = false, anyLe = false;
+        LambdaIter li(lambdaU);
+        for (int k = 0; k < kNLambda; ++k, li.Next()) {
+            float r_e = io.Ru(k) * (sigT[k] * majScale) * T_maj[k] / pdf;
+            sumRe += r_e;
+            anyRe |= r_e != 0;
+            anyLe |= scale * SpectrumAt(rs.spectra[m.le], li.lam) != 0;
+        }
+        if (!anyLe || !anyRe) return;
+        const float avg = sumRe / kNLambda;
+        LambdaIter lj(lambdaU);
+        for (int k = 0; k < kNLambda; ++k, lj.Next()) {
+            float Le = scale * SpectrumAt(rs.spectra[m.le], lj.lam);
+            float betap = io.Beta(k) * T_maj[k] / pdf;
+            io.AddL(k, betap * (sigA[k] * density) * Le / avg);
+        }
+    }
     B2_HD bool AnyBeta() const {
         bool any = false;
 B2_SPECTRAL_LOOP
@@ -389,6 +435,7 @@ B2_SPECTRAL_LOOP
             terminated = true;
             return false;
         }
+        if (m.emissive && depth < maxDepth) AddEmission(p, density, majScale, T_maj);
         const float sigMaj0 = sigT[0] * majScale;
         float pAbsorb = (sigA[0] * density) / sigMaj0;
         float pScat = (sigS[0] * density) / sigMaj0;

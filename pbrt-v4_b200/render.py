@@ -202,6 +202,14 @@ class RenderScene:
                     maj = np.ascontiguousarray(d[f"medium_majorants_{k}"], np.float32).reshape(-1)
                     m.density, m.majorants = capi.fptr(dens), capi.fptr(maj)
                     keep += [dens, maj]
+                if "media_le" in d and int(d["media_le"].reshape(-1, 4)[k][0]) >= 0:  # emissive: Le_spec, LeScale grid
+                    le = d["media_le"].reshape(-1, 4)[k]
+                    m.emissive, m.le_spectrum = 1, int(le[0])
+                    if m.type == 1:
+                        lg = np.ascontiguousarray(d[f"medium_lescale_{k}"], np.float32).reshape(-1)
+                        m.le_nx, m.le_ny, m.le_nz = int(le[1]), int(le[2]), int(le[3])
+                        m.le_scale = capi.fptr(lg)
+                        keep.append(lg)
             mm = np.ascontiguousarray(d["mesh_media"], np.int32).reshape(-1)
             r.n_media, r.media = len(mi), media
             r.mesh_media = mm.ctypes.data_as(C.POINTER(C.c_int32))

@@ -931,7 +931,8 @@ def with_density_grid(d, density, medium=0):
 
 
 def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm", seed=0, grid=256, density=None,
-                 fog=True, crop=None, lightsampler="bvh", patch_cap=False, lights=(), sampler="zsobol", envmap=0):
+                 fog=True, crop=None, lightsampler="bvh", patch_cap=False, lights=(), sampler="zsobol", envmap=0,
+                 emissive=False):
     """BASELINE configs[4]: VolPathIntegrator in the Cornell room: a thin homogeneous fog fills the room (an
     `interface` quad closes the open front; the camera stays in vacuum: a camera medium trips a race in the
     reference's BasicScene::GetMedium / CreateMedia, scene.cpp:809-850), and a box-shaped `interface` shell
@@ -955,7 +956,9 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
     outside = '"fog"' if fog else '""'
     if fog:
         lines += ['MakeNamedMedium "fog" "string type" "homogeneous" "rgb sigma_a" [0.02 0.02 0.03] '
-                  '"rgb sigma_s" [0.25 0.25 0.3] "float scale" 1 "float g" 0.3',
+                  '"rgb sigma_s" [0.25 0.25 0.3] "float scale" 1 "float g" 0.3'
+                  # emissive: a faintly glowing fog (HomogeneousMedium's Le, media.h:217-262)
+                  + (' "rgb Le" [0.5 0.7 1.0] "float Lescale" 0.4' if emissive else ''),
                   # front cap, normal towards the camera (-z): fog behind it, vacuum in front
                   'AttributeBegin', '  MediumInterface "fog" ""', '  Material "interface"',
                   # patch_cap: the same quad as ONE bilinear patch (medium transitions by a patch's normal)
@@ -964,7 +967,14 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
     lo, hi = (0.22, 0.18, 0.25), (0.78, 0.74, 0.81)
     lines.append(f'MakeNamedMedium "cloud" "string type" "uniformgrid" "integer nx" {nx} "integer ny" {ny} "integer nz" {nz} '
                  f'"point3 p0" [{lo[0]} {lo[1]} {lo[2]}] "point3 p1" [{hi[0]} {hi[1]} {hi[2]}] '
-                 '"rgb sigma_a" [0.5 0.5 0.5] "rgb sigma_s" [14 14 15] "float scale" 1 "float g" 0.6 "float density" [')
+                 '"rgb sigma_a" [0.5 0.5 0.5] "rgb sigma_s" [14 14 15] "float scale" 1 "float g" 0.6 '
+                 # emissive: the cloud glows where an LeScale grid of its own resolution says so (GridMedium, media.h:301-318);
+                 # "half" = no "Lescale" array (the reference then makes a 1 x 1 x 1 grid: a tent over the bounds under its
+                 # trilinear lookup with zeros outside)
+                 + (('"rgb Le" [1.0 0.55 0.2] ' + ('' if emissive == "half" else '"float Lescale" [' + " ".join(
+                     f"{v:.5g}" for v in np.clip(np.sin(np.arange(nx * ny * nz) * 0.37) * 3.0, 0.0, None)) + '] '))
+                    if emissive else '')
+                 + '"float density" [')
     key = (dens.shape, hash(dens.tobytes()))
     if _DENSITY_TEXT.get("key") != key:  # formatting 256^3 values takes ~10 s: keep the last grid's text
         flat = dens.reshape(-1)

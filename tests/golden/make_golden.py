@@ -240,6 +240,10 @@ TIGHT_CASES = {
     "tight_envmap": ("cornell", dict(res=32, spp=4096, maxdepth=5, lightsampler="bvh", envmap=32,
                                      boxes=(None, "conductor_smooth"))),
     "tight_envmap_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=8192, envmap=32)),
+    # emissive media (sigma_a * Le at every tentative collision, cpu/integrators.cpp:990-1001): a glowing fog and a cloud with
+    # an LeScale grid of the density's resolution; and with one Lescale number (a 1 x 1 x 1 grid)
+    "tight_emissive_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096, emissive=True)),
+    "tight_emissive_vol1": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096, emissive="half")),
     "tight_envmap_power": ("cornell", dict(res=32, spp=4096, maxdepth=4, lightsampler="power", envmap=32)),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),

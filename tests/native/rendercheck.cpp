@@ -144,6 +144,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
     for (size_t i = 0; i < rh.media.size(); ++i) {
         rh.media[i].density = rh.mediumGrids[i].first.data();
         rh.media[i].majorants = rh.mediumGrids[i].second.data();
+        rh.media[i].leScale = rh.mediumLeGrids[i].empty() ? nullptr : rh.mediumLeGrids[i].data();
     }
     rs.media = rh.media.data();
     const int W = rh.width, H = rh.height;
@@ -207,6 +208,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
     for (size_t i = 0; i < rh.media.size(); ++i) {
         rh.media[i].density = rh.mediumGrids[i].first.data();
         rh.media[i].majorants = rh.mediumGrids[i].second.data();
+        rh.media[i].leScale = rh.mediumLeGrids[i].empty() ? nullptr : rh.mediumLeGrids[i].data();
     }
     rs.media = rh.media.data();
     int full = rs.integrator.maxDepth;
