@@ -255,8 +255,8 @@ typedef struct b200pt_mesh_attr {
     /* TriangleMesh::n / ::uv (util/mesh.h:44-47) of a triangle mesh, one entry per triangle CORNER in index order
      * (3 x 3 floats, 3 x 2 floats per triangle), or NULL: shading normals and the (u,v) parameterisation of
      * Triangle::InteractionFromIntersection (shapes.h:884-1010).  A bilinear patch mesh takes corner_n with FOUR
-     * entries per patch (4 x 3 floats, index order p00 p10 p01 p11: BilinearPatchMesh::n, shapes.h:1474-1494);
-     * its corner_uv is ignored. */
+     * entries per patch (4 x 3 floats, index order p00 p10 p01 p11: BilinearPatchMesh::n, shapes.h:1474-1494) and
+     * corner_uv likewise (4 x 2 floats: BilinearPatchMesh::uv, the (s, t) that dpdu / dpdv follow, shapes.h:1412-1440). */
     const float *corner_n;
     const float *corner_uv;
     /* TriangleMesh::s, the per-vertex shading tangents (shapes.h:950-959), per corner like corner_n (3 x 3 floats per

@@ -490,17 +490,20 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
         if (meshRemap[m] < 0) continue;
         if (m >= nTriMeshes) {
             const BilinearPatchMesh *mesh = patchMesh(m);
-            if (mesh->uv) die("per-vertex uv on bilinear patch meshes is not dumped");
             if (mesh->imageDistribution) die("image-distributed patch emission is not dumped");
             nv.push_back(mesh->nVertices);
             nt.push_back(mesh->nPatches);
             meshKind.push_back(1);
             meshHasN.push_back(mesh->n ? 1 : 0);  // four corner normals per patch
-            meshHasUV.push_back(0);
+            meshHasUV.push_back(mesh->uv ? 1 : 0);  // four corner (s, t) per patch
             meshHasS.push_back(0);
             for (int i = 0; mesh->n && i < 4 * mesh->nPatches; ++i) {
                 const Normal3f &vn = mesh->n[mesh->vertexIndices[i]];
                 cornerN.insert(cornerN.end(), {vn.x, vn.y, vn.z});
+            }
+            for (int i = 0; mesh->uv && i < 4 * mesh->nPatches; ++i) {
+                const Point2f &st = mesh->uv[mesh->vertexIndices[i]];
+                cornerUV.insert(cornerUV.end(), {st.x, st.y});
             }
             for (int i = 0; i < mesh->nVertices; ++i) P.insert(P.end(), {mesh->p[i].x, mesh->p[i].y, mesh->p[i].z});
             patchIdx.insert(patchIdx.end(), mesh->vertexIndices, mesh->vertexIndices + 4 * mesh->nPatches);

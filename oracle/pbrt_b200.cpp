@@ -277,7 +277,7 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
         }
         if (hasUV && hasUV[i]) {
             A.corner_uv = T.at("corner_uv").f() + 2 * uvAt;
-            uvAt += 3 * size_t(ntris[i]);
+            uvAt += ((kind && kind[i] == 1) ? 4 : 3) * size_t(ntris[i]);
         }
         if (hasS && hasS[i]) {
             A.corner_s = T.at("corner_s").f() + 3 * sAt;

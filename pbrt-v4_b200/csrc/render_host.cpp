@@ -308,14 +308,14 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         uint32_t nOff = kNoCornerAttr, uvOff = kNoCornerAttr, sOff = kNoCornerAttr;
         if (m.corner_n || m.corner_uv || m.corner_s) {
             const bool patch = (meshKind[i] & 1) != 0;  // four corners per patch, normals only
-            if (out.cornerAttr.size() + 27 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
+            if (out.cornerAttr.size() + 29 * size_t(meshTris[i]) >= size_t(kNoCornerAttr)) return bad("too many per-corner attributes");
             if (m.corner_n) {
                 nOff = uint32_t(out.cornerAttr.size());
                 out.cornerAttr.insert(out.cornerAttr.end(), m.corner_n, m.corner_n + (patch ? 12 : 9) * size_t(meshTris[i]));
             }
-            if (m.corner_uv && !patch) {
+            if (m.corner_uv) {  // three (s, t) per triangle, four per patch
                 uvOff = uint32_t(out.cornerAttr.size());
-                out.cornerAttr.insert(out.cornerAttr.end(), m.corner_uv, m.corner_uv + 6 * size_t(meshTris[i]));
+                out.cornerAttr.insert(out.cornerAttr.end(), m.corner_uv, m.corner_uv + (patch ? 8 : 6) * size_t(meshTris[i]));
             }
             if (m.corner_s && !patch) {
                 sOff = uint32_t(out.cornerAttr.size());

@@ -48,7 +48,7 @@ struct CornerAttr {
 B2_HD CornerAttr CornersOf(const RenderSceneDev &rs, const MeshAttrDev &mesh, uint32_t tri, uint32_t kind = 0) {
     CornerAttr c;  // a bilinear patch has four corners (normals only)
     c.n = mesh.nOff != kNoCornerAttr ? rs.cornerAttr + mesh.nOff + ((kind & 1) ? 12 : 9) * size_t(tri) : nullptr;
-    c.uv = mesh.uvOff != kNoCornerAttr ? rs.cornerAttr + mesh.uvOff + 6 * size_t(tri) : nullptr;
+    c.uv = mesh.uvOff != kNoCornerAttr ? rs.cornerAttr + mesh.uvOff + ((kind & 1) ? 8 : 6) * size_t(tri) : nullptr;
     c.s = (mesh.sOff != kNoCornerAttr && !(kind & 1)) ? rs.cornerAttr + mesh.sOff + 9 * size_t(tri) : nullptr;
     return c;
 }
@@ -144,13 +144,30 @@ B2_HD void RotateFromTo(V3 from, V3 to, float r[3][3]) {
                       4 * Dot(u, v) / (Dot(u, u) * Dot(v, v)) * vv[i] * uu[j];
 }
 
-B2_HD_CALL SurfHit PatchInteraction(const PatchVerts &t, float u, float v, V3 wo, bool flipNormal, const float *cn = nullptr) {
+// cuv: the corners' (s, t) in index order p00 p10 p01 p11 (BilinearPatchMesh::uv), or null
+B2_HD_CALL SurfHit PatchInteraction(const PatchVerts &t, float u, float v, V3 wo, bool flipNormal, const float *cn = nullptr,
+                                    const float *cuv = nullptr) {
     SurfHit h;
     const V3 p00 = t.p0, p10 = t.p1, p01 = t.p2, p11 = t.p3;
     V3 e0 = (1 - v) * p00 + v * p01, e1 = (1 - v) * p10 + v * p11;
     V3 p = (1 - u) * e0 + u * e1;
     V3 dpdu = e1 - e0;
     V3 dpdv = ((1 - u) * p01 + u * p11) - ((1 - u) * p00 + u * p10);
+    if (cuv) {  // dpdu / dpdv with respect to the mesh's own (s, t) (shapes.h:1412-1440)
+        const float s00 = cuv[0], t00 = cuv[1], s10 = cuv[2], t10 = cuv[3], s01 = cuv[4], t01 = cuv[5], s11 = cuv[6], t11 = cuv[7];
+        const float dsdu = Lerp(v, s10, s11) - Lerp(v, s00, s01), dtdu = Lerp(v, t10, t11) - Lerp(v, t00, t01);
+        const float dsdv = Lerp(u, s01, s11) - Lerp(u, s00, s10), dtdv = Lerp(u, t01, t11) - Lerp(u, t00, t10);
+        const float duds = fabsf(dsdu) < 1e-8f ? 0 : 1 / dsdu, dvds = fabsf(dsdv) < 1e-8f ? 0 : 1 / dsdv;
+        const float dudt = fabsf(dtdu) < 1e-8f ? 0 : 1 / dtdu, dvdt = fabsf(dtdv) < 1e-8f ? 0 : 1 / dtdv;
+        V3 dpds = dpdu * duds + dpdv * dvds;
+        V3 dpdt = dpdu * dudt + dpdv * dvdt;
+        V3 c = Cross(dpds, dpdt);
+        if (c.x != 0 || c.y != 0 || c.z != 0) {
+            if (Dot(Cross(dpdu, dpdv), c) < 0) dpdt = -dpdt;
+            dpdu = dpds;
+            dpdv = dpdt;
+        }
+    }
     V3 pAbsSum = Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11);
     h.pi = MakeP3i(p, GammaF(6) * pAbsSum);
     h.u = u;
@@ -184,7 +201,7 @@ B2_HD SurfHit SlotInteraction(const void *prims, uint32_t slot, const TriVerts &
     if (EXT == 0) return TriangleInteraction(t, b0, b1, b2, wo, flipNormal);
     if (t.kind & 1) {
         const PatchVerts pv = LoadPatch(prims, slot);
-        return PatchInteraction(pv, b1, b2, wo, flipNormal, ca.n);
+        return PatchInteraction(pv, b1, b2, wo, flipNormal, ca.n, ca.uv);
     }
     return TriangleInteraction(t, b0, b1, b2, wo, flipNormal, ca);
 }

@@ -171,8 +171,9 @@ class RenderScene:
                 meshes[i].corner_n = capi.fptr(cn)
                 keep.append(cn)
             if has_uv[i]:
-                cuv = np.ascontiguousarray(d["corner_uv"][uv_at:uv_at + 3 * ntris[i]], np.float32)
-                uv_at += 3 * int(ntris[i])
+                per = 4 if "mesh_kind" in d and d["mesh_kind"][i] == 1 else 3
+                cuv = np.ascontiguousarray(d["corner_uv"][uv_at:uv_at + per * ntris[i]], np.float32)
+                uv_at += per * int(ntris[i])
                 meshes[i].corner_uv = capi.fptr(cuv)
                 keep.append(cuv)
             if has_s[i]:  # per-vertex shading tangents

@@ -508,11 +508,15 @@ def cornell_pbrt(path, res=512, spp=64, maxdepth=5, lightsampler="power", out="c
                         nv = np.array([-dx, 1.0, -dz])
                         nrm.append(nv / np.linalg.norm(nv))
                 txt += f' "normal N" [{" ".join(f"{float(c):.7g}" for nv in nrm for c in nv)}]'
+            if patches == "uv":  # a skewed, slightly non-affine (s, t) of its own (BilinearPatchMesh::uv): dpdu / dpdv follow it
+                st = [(0.7 * u + 0.5 * v + 0.2 * u * v, -0.3 * u + 0.9 * v) for v in g for u in g]
+                txt += f' "point2 uv" [{" ".join(f"{float(c):.7g}" for q in st for c in q)}]'
             return txt
-        lines += ['AttributeBegin', '  Material "diffuse" "rgb reflectance" [0.25 0.35 0.75]',
+        lines += ['AttributeBegin', ('  ' + MATERIALS["conductor_reflectance"]) if patches == "uv" else
+                  '  Material "diffuse" "rgb reflectance" [0.25 0.35 0.75]',
                   '  ' + sheet(0.5, 0.92, 0.12, 0.55, 4, lambda u, v: 0.42 + 0.07 * np.sin(5.0 * u) * np.cos(4.0 * v) + 0.1 * u * v),
                   'AttributeEnd',
-                  'AttributeBegin', '  ' + MATERIALS["conductor_rough"], '  ReverseOrientation',
+                  'AttributeBegin', '  ' + MATERIALS["conductor_reflectance" if patches == "uv" else "conductor_rough"], '  ReverseOrientation',
                   '  ' + sheet(0.05, 0.3, 0.1, 0.45, 1, lambda u, v: 0.75 + 0.18 * (2 * u - 1) * (2 * v - 1)),
                   'AttributeEnd']
         if patches == "normals":

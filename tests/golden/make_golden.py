@@ -89,6 +89,8 @@ RENDER_CASES = {
     "cornell_alpha_r64_s16": dict(res=64, spp=16, maxdepth=5, alpha=True),
     # vertex normals on bilinear patches: shading geometry of a wavy sheet, an emitter oriented by its normals
     "cornell_patchnormals_r64_s16": dict(res=64, spp=16, maxdepth=5, patches="normals"),
+    # per-vertex (s, t) on bilinear patches under anisotropic metal: the shading frame follows the mesh's parameterisation
+    "cornell_patchuv_r64_s16": dict(res=64, spp=16, maxdepth=5, patches="uv"),
     "cornell_patchlights_r64_s16": dict(res=64, spp=16, maxdepth=5, patches="emissive", lightsampler="bvh"),
 }
 # Cases whose gate is the Monte-Carlo noise floor (rRMSE(ours, ref) <= 1.25 x rRMSE(ref seed s,

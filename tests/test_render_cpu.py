@@ -40,6 +40,7 @@ def _check(P, rendercheck, name, **kw):
                                   "cornell_smooth_r64_s16",  # per-vertex normals + uv (shading geometry)
                                   "cornell_smoothinst_r64_s16",  # ... on an object instanced under rotation + scale
                                   "cornell_tangents_r64_s16",  # per-vertex tangents, with and without normals
+                                  "cornell_patchuv_r64_s16",  # per-vertex (s, t) on bilinear patches
                                   "cornell_alpha_r64_s16",  # constant alpha cut-outs
                                   "cornell_patchnormals_r64_s16"])  # vertex normals on bilinear patches
 def test_golden_image(P, rendercheck, name):

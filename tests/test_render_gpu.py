@@ -23,7 +23,7 @@ def cornell(P):
 @pytest.mark.parametrize("name", ["cornell_r64_s16", "cornell_r48_s8_uniform", "cornell_metal_r64_s16",
                                   "cornell_metal2_r48_s8", "cornell_glass_r64_s16", "cornell_instanced_r64_s16", "cornell_manylights_r64_s16",
                                   "cornell_infinite_r64_s16", "cornell_infinite_power_r48_s8", "cornell_coated_r64_s16", "config3_small",
-                                  "cornell_patches_r64_s16", "cornell_patchlights_r64_s16", "cornell_smooth_r64_s16", "cornell_smoothinst_r64_s16", "cornell_tangents_r64_s16", "cornell_alpha_r64_s16",
+                                  "cornell_patches_r64_s16", "cornell_patchlights_r64_s16", "cornell_smooth_r64_s16", "cornell_smoothinst_r64_s16", "cornell_tangents_r64_s16", "cornell_patchuv_r64_s16", "cornell_alpha_r64_s16",
                                   "cornell_patchnormals_r64_s16"])
 @pytest.mark.parametrize("host_bvh", [False, True])
 def test_golden_image(P, name, host_bvh):
