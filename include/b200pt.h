@@ -288,11 +288,15 @@ typedef struct b200pt_medium {
      * tentative collision, sigma_a * Le (cpu/integrators.cpp:990-1001).  le_spectrum = Le_spec (a homogeneous medium's
      * already times its Lescale / photometric normalisation, as the object holds it).  Grid media: le_scale = the LeScale
      * grid, le_nx x le_ny x le_nz values (1 x 1 x 1 when the scene gave no "Lescale" array; trilinear with zeros outside,
-     * like the density).  Temperature grids (blackbody emission) are not taken. */
+     * like the density).  temperature != NULL: a grid of the density's resolution; where (T - temperature_offset) *
+     * temperature_scale > 100 the emission is le_scale times the normalised blackbody spectrum of that temperature
+     * instead of Le_spec (media.h:306-314; le_spectrum is then unused but must be a valid index). */
     uint32_t emissive;
     int32_t le_spectrum;
     int32_t le_nx, le_ny, le_nz;
     const float *le_scale;
+    const float *temperature;
+    float temperature_scale, temperature_offset;
 } b200pt_medium;
 
 typedef struct b200pt_render_desc {

@@ -595,7 +595,12 @@ void FlattenScene(RefObjects &ro, W &w, bool dumpBvh, size_t *nMeshOut = nullptr
                 w.f32("medium_density_" + std::to_string(k), {uint32_t(dg.nz), uint32_t(dg.ny), uint32_t(dg.nx)}, dens);
                 w.f32("medium_majorants_" + std::to_string(k), {uint32_t(mg.res.z), uint32_t(mg.res.y), uint32_t(mg.res.x)}, maj);
                 if (m.IsEmissive()) {
-                    if (gm->temperatureGrid) die("grid media with a temperature grid (blackbody emission) are not dumped");
+                    if (gm->temperatureGrid) {  // blackbody emission: the grid and its scale / offset
+                        const SampledGrid<Float> &tg = *gm->temperatureGrid;
+                        std::vector<float> tv(tg.values.begin(), tg.values.end());
+                        w.f32("medium_temperature_" + std::to_string(k), {uint32_t(tg.nz), uint32_t(tg.ny), uint32_t(tg.nx)}, tv);
+                        w.f32("medium_temperature_params_" + std::to_string(k), {2}, {gm->temperatureScale, gm->temperatureOffset});
+                    }
                     const SampledGrid<Float> &lg = gm->LeScale;
                     le[0] = pool.add(&gm->Le_spec, 0);
                     le[1] = lg.nx;

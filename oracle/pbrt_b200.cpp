@@ -325,6 +325,11 @@ static void MarshalRender(const MemTables &T, Marshalled &m) {
                     M.le_ny = le[2];
                     M.le_nz = le[3];
                     M.le_scale = T.at("medium_lescale_" + std::to_string(k)).f();
+                    if (T.has("medium_temperature_" + std::to_string(k))) {
+                        M.temperature = T.at("medium_temperature_" + std::to_string(k)).f();
+                        M.temperature_scale = T.at("medium_temperature_params_" + std::to_string(k)).f()[0];
+                        M.temperature_offset = T.at("medium_temperature_params_" + std::to_string(k)).f()[1];
+                    }
                 }
             }
         }

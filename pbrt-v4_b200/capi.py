@@ -192,7 +192,8 @@ class Medium(C.Structure):
                 ("render_from_medium", C.c_float * 16), ("nx", C.c_int32), ("ny", C.c_int32), ("nz", C.c_int32),
                 ("density", C.POINTER(C.c_float)), ("mres", C.c_int32 * 3), ("majorants", C.POINTER(C.c_float)),
                 ("emissive", C.c_uint32), ("le_spectrum", C.c_int32), ("le_nx", C.c_int32), ("le_ny", C.c_int32),
-                ("le_nz", C.c_int32), ("le_scale", C.POINTER(C.c_float))]
+                ("le_nz", C.c_int32), ("le_scale", C.POINTER(C.c_float)), ("temperature", C.POINTER(C.c_float)),
+                ("temperature_scale", C.c_float), ("temperature_offset", C.c_float)]
 
 
 class RenderDesc(C.Structure):

@@ -139,6 +139,12 @@ int b200pt_render_create(b200pt_scene *scene, const b200pt_render_desc *desc, b2
             r->dGrids.push_back(dl);
             r->host.media[i].leScale = (const float *)dl;
         }
+        if (!r->host.mediumTempGrids[i].empty()) {
+            void *dt = nullptr;
+            if ((rc = Upload(ctx, r->host.mediumTempGrids[i], &dt))) return fail(rc);
+            r->dGrids.push_back(dt);
+            r->host.media[i].temperature = (const float *)dt;
+        }
     }
     if ((rc = Upload(ctx, r->host.media, &r->dMedia))) return fail(rc);
     r->nPixels = r->host.width * r->host.height;

@@ -200,6 +200,7 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
         out.media.resize(d->n_media);
         out.mediumGrids.resize(d->n_media);
         out.mediumLeGrids.resize(d->n_media);
+        out.mediumTempGrids.resize(d->n_media);
         for (uint32_t i = 0; i < d->n_media; ++i) {
             const b200pt_medium &m = d->media[i];
             if (m.type > B200PT_MEDIUM_GRID) return bad("unsupported medium type");
@@ -230,6 +231,11 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                     if (m.le_nx < 1 || m.le_ny < 1 || m.le_nz < 1 || !m.le_scale) return bad("emissive grid medium without an LeScale grid");
                     o.lnx = m.le_nx; o.lny = m.le_ny; o.lnz = m.le_nz;
                     out.mediumLeGrids[i].assign(m.le_scale, m.le_scale + size_t(m.le_nx) * m.le_ny * m.le_nz);
+                    if (m.temperature) {
+                        out.mediumTempGrids[i].assign(m.temperature, m.temperature + size_t(m.nx) * m.ny * m.nz);
+                        o.temperatureScale = m.temperature_scale;
+                        o.temperatureOffset = m.temperature_offset;
+                    }
                 }
             }
         }

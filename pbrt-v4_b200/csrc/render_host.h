@@ -25,6 +25,7 @@ struct RenderHost {
     std::vector<float> lightGeom;          // delta lights' placement, kLightGeomFloats per light; empty = none
     std::vector<MediumDev> media;          // density / majorants pointers are filled by the owner of the grids
     std::vector<std::pair<std::vector<float>, std::vector<float>>> mediumGrids;  // per medium: density, majorants
+    std::vector<std::vector<float>> mediumTempGrids;  // per medium: the temperature grid (else empty)
     std::vector<std::vector<float>> mediumLeGrids;  // per medium: the LeScale grid of an emissive grid medium (else empty)
     std::vector<float> cornerAttr;         // per-corner normals / uv (MeshAttrDev::nOff, uvOff)
     std::vector<float> lens, pupilBounds;  // realistic camera: 4 floats per element / per film-radius bin

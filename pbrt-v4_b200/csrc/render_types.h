@@ -83,6 +83,10 @@ struct MediumDev {
     int32_t le;
     int32_t lnx, lny, lnz;
     const float *leScale;  // null: homogeneous
+    // a grid medium's temperature grid (the density's resolution): blackbody emission instead of Le_spec where
+    // (T - temperatureOffset) * temperatureScale > 100 K (media.h:306-314); null = none
+    const float *temperature;
+    float temperatureScale, temperatureOffset;
 };
 
 struct CameraDev {

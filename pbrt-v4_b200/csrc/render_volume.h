@@ -78,14 +78,30 @@ B2_HD V3 BoundsOffset(const float *b, V3 p) {
     if (b[5] > b[2]) o.z /= b[5] - b[2];
     return o;
 }
-// GridMedium's LeScale.Lookup(p) at a render-space point (media.h:303-305): the same trilinear lookup, zero outside
-B2_HD float MediumLeScaleAt(const MediumDev &m, V3 p) {
+// Blackbody(lambda, T) and BlackbodySpectrum(T)(lambda) (util/spectrum.h:69-80, 530-545)
+B2_HD float Blackbody(float lambda, float T) {
+    if (T <= 0) return 0;
+    const float c = 299792458.f, h = 6.62606957e-34f, kb = 1.3806488e-23f;
+    float l = lambda * 1e-9f;
+    float l2 = l * l, l5 = (l2 * l2) * l;  // Pow<5>
+    return (2 * h * c * c) / (l5 * (FastExpRef((h * c) / (l * kb * T)) - 1));
+}
+B2_HD float BlackbodyNormalized(float lambda, float T) {
+    float lambdaMax = 2.8977721e-3f / T;
+    float normalizationFactor = 1 / Blackbody(lambdaMax * 1e9f, T);
+    return Blackbody(lambda, T) * normalizationFactor;
+}
+// SampledGrid<Float>::Lookup of an emissive grid medium's LeScale (which = 0; its own resolution) or temperature grid
+// (which = 1; the density's resolution) at a render-space point (media.h:303-308): trilinear, zero outside
+B2_HD float MediumLeScaleAt(const MediumDev &m, V3 p, int which = 0) {
     V3 q = BoundsOffset(m.bounds, XformPoint(m.mediumFromRender, p));
+    const float *grid = which ? m.temperature : m.leScale;
+    const int gx = which ? m.nx : m.lnx, gy = which ? m.ny : m.lny, gz = which ? m.nz : m.lnz;
     auto at = [&](int x, int y, int z) -> float {
-        if (x < 0 || y < 0 || z < 0 || x >= m.lnx || y >= m.lny || z >= m.lnz) return 0.f;
-        return m.leScale[((long long)z * m.lny + y) * m.lnx + x];
+        if (x < 0 || y < 0 || z < 0 || x >= gx || y >= gy || z >= gz) return 0.f;
+        return grid[((long long)z * gy + y) * gx + x];
     };
-    float sx = q.x * m.lnx - .5f, sy = q.y * m.lny - .5f, sz = q.z * m.lnz - .5f;
+    float sx = q.x * gx - .5f, sy = q.y * gy - .5f, sz = q.z * gz - .5f;
     float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
     int ix = (int)fx, iy = (int)fy, iz = (int)fz;
     float dx = sx - fx, dy = sy - fy, dz = sz - fz;
@@ -395,9 +411,14 @@ struct PathMediumCB {
     // "Add emission from medium scattering event" (cpu/integrators.cpp:990-1001): at EVERY tentative collision
     B2_HD void AddEmission(V3 p, float density, float majScale, const float *T_maj) {
         float scale = 1.f;
+        float temp = 0;  // > 0: blackbody emission at that temperature instead of Le_spec
         if (m.leScale) {  // GridMedium::SamplePoint (media.h:301-318): nothing where LeScale <= 0
             scale = MediumLeScaleAt(m, p);
             if (!(scale > 0)) return;
+            if (m.temperature) {
+                temp = (MediumLeScaleAt(m, p, 1) - m.temperatureOffset) * m.temperatureScale;
+                if (!(temp > 100.f)) return;
+            }
         }
         const float pdf = (sigT[0] * majScale) * T_maj[0];
         float sumRe = 0;
@@ -407,13 +428,13 @@ struct PathMediumCB {
             float r_e = io.Ru(k) * (sigT[k] * majScale) * T_maj[k] / pdf;
             sumRe += r_e;
             anyRe |= r_e != 0;
-            anyLe |= scale * SpectrumAt(rs.spectra[m.le], li.lam) != 0;
+            anyLe |= scale * (temp > 0 ? BlackbodyNormalized(li.lam, temp) : SpectrumAt(rs.spectra[m.le], li.lam)) != 0;
         }
         if (!anyLe || !anyRe) return;
         const float avg = sumRe / kNLambda;
         LambdaIter lj(lambdaU);
         for (int k = 0; k < kNLambda; ++k, lj.Next()) {
-            float Le = scale * SpectrumAt(rs.spectra[m.le], lj.lam);
+            float Le = scale * (temp > 0 ? BlackbodyNormalized(lj.lam, temp) : SpectrumAt(rs.spectra[m.le], lj.lam));
             float betap = io.Beta(k) * T_maj[k] / pdf;
             io.AddL(k, betap * (sigA[k] * density) * Le / avg);
         }

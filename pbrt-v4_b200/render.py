@@ -211,6 +211,11 @@ class RenderScene:
                         m.le_nx, m.le_ny, m.le_nz = int(le[1]), int(le[2]), int(le[3])
                         m.le_scale = capi.fptr(lg)
                         keep.append(lg)
+                        if f"medium_temperature_{k}" in d:  # blackbody emission from a temperature grid
+                            tg = np.ascontiguousarray(d[f"medium_temperature_{k}"], np.float32).reshape(-1)
+                            m.temperature = capi.fptr(tg)
+                            m.temperature_scale, m.temperature_offset = (float(x) for x in d[f"medium_temperature_params_{k}"])
+                            keep.append(tg)
             mm = np.ascontiguousarray(d["mesh_media"], np.int32).reshape(-1)
             r.n_media, r.media = len(mi), media
             r.mesh_media = mm.ctypes.data_as(C.POINTER(C.c_int32))

@@ -975,8 +975,12 @@ def config5_pbrt(path, res=(1920, 1080), spp=512, maxdepth=5, out="config5.pfm",
                  # emissive: the cloud glows where an LeScale grid of its own resolution says so (GridMedium, media.h:301-318);
                  # "half" = no "Lescale" array (the reference then makes a 1 x 1 x 1 grid: a tent over the bounds under its
                  # trilinear lookup with zeros outside)
-                 + (('"rgb Le" [1.0 0.55 0.2] ' + ('' if emissive == "half" else '"float Lescale" [' + " ".join(
-                     f"{v:.5g}" for v in np.clip(np.sin(np.arange(nx * ny * nz) * 0.37) * 3.0, 0.0, None)) + '] '))
+                 # "blackbody" = a temperature grid (800 .. 4000 on its own scale, with temperaturescale / offset) instead of Le
+                 + ('"float temperature" [' + " ".join(f"{v:.6g}" for v in 2400.0 + 1600.0 * np.sin(np.arange(nx * ny * nz) * 0.11))
+                    + '] "float temperaturescale" 0.9 "float temperatureoffset" 150 "float Lescale" ['
+                    + " ".join(f"{v:.5g}" for v in np.full(nx * ny * nz, 1.5)) + '] ' if emissive == "blackbody" else
+                    ('"rgb Le" [1.0 0.55 0.2] ' + ('' if emissive == "half" else '"float Lescale" [' + " ".join(
+                        f"{v:.5g}" for v in np.clip(np.sin(np.arange(nx * ny * nz) * 0.37) * 3.0, 0.0, None)) + '] '))
                     if emissive else '')
                  + '"float density" [')
     key = (dens.shape, hash(dens.tobytes()))

@@ -246,6 +246,7 @@ TIGHT_CASES = {
     # an LeScale grid of the density's resolution; and with one Lescale number (a 1 x 1 x 1 grid)
     "tight_emissive_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096, emissive=True)),
     "tight_emissive_vol1": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096, emissive="half")),
+    "tight_blackbody_vol": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096, emissive="blackbody")),
     "tight_envmap_power": ("cornell", dict(res=32, spp=4096, maxdepth=4, lightsampler="power", envmap=32)),
     "tight_config3": ("config3", dict(CONFIG3_SMALL, res=(32, 18), spp=16384)),
     "tight_config5": ("config5", dict(CONFIG5_SMALL, res=(32, 24), spp=4096)),

@@ -145,6 +145,7 @@ extern "C" int rendercheck_run(const b200pt_scene_desc *sd, const b200pt_render_
         rh.media[i].density = rh.mediumGrids[i].first.data();
         rh.media[i].majorants = rh.mediumGrids[i].second.data();
         rh.media[i].leScale = rh.mediumLeGrids[i].empty() ? nullptr : rh.mediumLeGrids[i].data();
+        rh.media[i].temperature = rh.mediumTempGrids[i].empty() ? nullptr : rh.mediumTempGrids[i].data();
     }
     rs.media = rh.media.data();
     const int W = rh.width, H = rh.height;
@@ -209,6 +210,7 @@ extern "C" int rendercheck_path(const b200pt_scene_desc *sd, const b200pt_render
         rh.media[i].density = rh.mediumGrids[i].first.data();
         rh.media[i].majorants = rh.mediumGrids[i].second.data();
         rh.media[i].leScale = rh.mediumLeGrids[i].empty() ? nullptr : rh.mediumLeGrids[i].data();
+        rh.media[i].temperature = rh.mediumTempGrids[i].empty() ? nullptr : rh.mediumTempGrids[i].data();
     }
     rs.media = rh.media.data();
     int full = rs.integrator.maxDepth;

@@ -246,7 +246,7 @@ def test_majorant_grid_mirror(P):
     np.testing.assert_array_equal(P.scenes.majorant_grid(d["medium_density_0"]), d["medium_majorants_0"])
 
 
-@pytest.mark.parametrize("name", ["tight_metal2", "tight_coated", "tight_alpha", "tight_glass", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power", "tight_independent", "tight_independent_vol", "tight_coatcond", "tight_coatcond2", "tight_envmap", "tight_envmap_power", "tight_envmap_vol", "tight_emissive_vol", "tight_emissive_vol1",
+@pytest.mark.parametrize("name", ["tight_metal2", "tight_coated", "tight_alpha", "tight_glass", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power", "tight_independent", "tight_independent_vol", "tight_coatcond", "tight_coatcond2", "tight_envmap", "tight_envmap_power", "tight_envmap_vol", "tight_emissive_vol", "tight_emissive_vol1", "tight_blackbody_vol",
                                   "tight_lights_vol"])
 def test_tight_noise_gate(P, rendercheck, name):
     """The 16-spp noise-gated families at 1024-4096 spp on a 32 x 32 frame (floor 2-5 %, make_golden.py TIGHT_CASES):

@@ -260,7 +260,7 @@ def test_volume_kernels_warp_per_ray_equals_thread_per_ray(P, monkeypatch):
     assert np.array_equal(films[0], films[1])
 
 
-TIGHT = ["tight_glass", "tight_metal2", "tight_coated", "tight_alpha", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power", "tight_lights_vol", "tight_independent", "tight_independent_vol", "tight_coatcond", "tight_coatcond2", "tight_envmap", "tight_envmap_power", "tight_envmap_vol", "tight_emissive_vol", "tight_emissive_vol1",
+TIGHT = ["tight_glass", "tight_metal2", "tight_coated", "tight_alpha", "tight_thin", "tight_dtrans", "tight_lights", "tight_lights_power", "tight_lights_vol", "tight_independent", "tight_independent_vol", "tight_coatcond", "tight_coatcond2", "tight_envmap", "tight_envmap_power", "tight_envmap_vol", "tight_emissive_vol", "tight_emissive_vol1", "tight_blackbody_vol",
          "tight_config3", "tight_config5"]
 
 
