@@ -1,5 +1,6 @@
 // render_host.cpp - validation + flattening of the render description (see render_host.h).
 #include "render_host.h"
+#include "render_lightbvh.h"
 
 #include <cmath>
 #include <cstring>
@@ -400,11 +401,14 @@ int BuildRenderTables(const b200pt_render_desc *d, const HostScene &hs, uint32_t
                            : ((link & 0x7FFFFFFFu) >= d->n_light_bvh_nodes || i + 1 >= d->n_light_bvh_nodes))
                 return bad("light BVH node refers outside its tables");
         }
-        out.lightBvhNodes.assign(nodes, nodes + 8 * size_t(d->n_light_bvh_nodes));
-        // allLightBounds rides behind the last node, so the sampler hands plain pointers to its helpers
-        uint32_t tail[8] = {};
-        std::memcpy(tail, d->light_bvh_bounds, 24);
-        out.lightBvhNodes.insert(out.lightBvhNodes.end(), tail, tail + 8);
+        // the device table: what CompactLightBounds::Importance derives from a node alone, worked out here once
+        // (render_lightbvh.h ExpandLightBvhNode; same float operations, this file is built without contraction)
+        out.lightBvhNodes.assign(size_t(kLightNodeWords) * d->n_light_bvh_nodes, 0u);
+        for (uint32_t i = 0; i < d->n_light_bvh_nodes; ++i) {
+            float e[kLightNodeWords];
+            ExpandLightBvhNode(nodes + 8 * size_t(i), d->light_bvh_bounds, e);
+            std::memcpy(&out.lightBvhNodes[size_t(kLightNodeWords) * i], e, sizeof e);
+        }
         out.lightBitTrails.assign(d->light_bit_trails, d->light_bit_trails + d->n_lights);
         rs.nLightBvhNodes = d->n_light_bvh_nodes;
         std::memcpy(rs.lightBvhBounds, d->light_bvh_bounds, 24);

@@ -17,7 +17,7 @@ struct RenderHost {
     std::vector<MaterialDev> materials;
     std::vector<LightDev> lights;
     std::vector<MeshAttrDev> meshes;
-    std::vector<uint32_t> lightBvhNodes;   // 8 per node
+    std::vector<uint32_t> lightBvhNodes;   // kLightNodeWords per node: the expanded nodes (render_lightbvh.h)
     std::vector<uint32_t> lightBitTrails;  // per light
     std::vector<int32_t> infiniteLights;   // light indices: the lights without bounds (BVHLightSampler's infiniteLights)
     std::vector<float> envImage, envDist;  // image infinite light: per-pixel spectrum coefficients, sampling distribution
