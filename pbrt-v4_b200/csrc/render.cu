@@ -342,7 +342,10 @@ ClassifyKernel(RenderSceneDev rs, PassBuffers pb, int depth) {
 #endif
 // ---- one path vertex: PathIntegrator::Li loop body (cpu/integrators.cpp:640-760)
 template <int MAT, int LBVH, int VOL, int EXT>
-__global__ void __launch_bounds__(kShadeBlock, B2_SHADE_MIN_BLOCKS)
+#ifndef B2_COATED_MIN_BLOCKS
+#define B2_COATED_MIN_BLOCKS 6  // the layered walks issue in 9 % of the slots: more warps beat fewer spills (config 3: 99.5 -> 101.8 Msamples/s)
+#endif
+__global__ void __launch_bounds__(kShadeBlock, MAT == (int)MAT_COATED_DIFFUSE ? B2_COATED_MIN_BLOCKS : B2_SHADE_MIN_BLOCKS)
 ShadeKernel(RenderSceneDev rs, PassBuffers pb, int depth, int nPixels, int width) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     int *counts = pb.counts + kCountStride * depth;
